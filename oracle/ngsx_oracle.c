@@ -1,0 +1,693 @@
+/* TEST INFRASTRUCTURE -- CPU oracle, not part of the product path.
+ *
+ * Plain-C restatement of the reference algorithm for the cut-FEM hot path
+ * (ngsxfem @ 88e7db38 + vendored NGSolve).  Every function cites the reference
+ * file:line it follows (paths relative to /root/reference; NGS/ =
+ * external_dependencies/ngsolve/).  Parity of this file is PINNED two ways
+ * (tests/test_oracle_*.py):
+ *   1. against the reference's own known-answer tests (tests/pytests/test_localgeom.py,
+ *      test_straightcutrule.py, test_xfes_ndof.py), and
+ *   2. against the reference's own sources compiled in place (oracle/_ref/libngsxref.so,
+ *      built by oracle/build_ref.sh) and the committed golden vectors made from it
+ *      (tests/golden/, tools/gen_golden.py).
+ *
+ * Only tests/, __graft_entry__.smoke() and bench.py's cpu_baseline / --impl reference leg
+ * may load this library.  Scalar, single-threaded unless a *_mesh entry point says otherwise.
+ */
+#include <math.h>
+#include <stdlib.h>
+#include <string.h>
+#include <stdint.h>
+#ifdef _OPENMP
+#include <omp.h>
+#endif
+#include "rule_tables.h"
+
+enum { NEG = 0, POS = 1, IF = 2 };          /* utils/ngsxstd.hpp:14-17 */
+enum { ORC_NULL = -1, ORC_THROW = -2, ORC_CAP = -3, ORC_UNSUP = -4 };
+
+/* ------------------------------------------------------------------ rule tables */
+/* NGS/fem/intrule.cpp:2620-2659 SelectIntegrationRule (data dumped from the compiled reference) */
+static int select_rule(int dim, int order, const double (**data)[4])
+{
+  if (order < 0) order = 0;
+  switch (dim) {
+  case 0: { static const double pt[1][4] = {{0, 0, 0, 1}}; *data = pt; return 1; }
+  case 1: if (order > NGSX_RULE_SEGM_MAXORDER) return ORC_UNSUP;
+    *data = NGSX_RULE_SEGM_DATA + NGSX_RULE_SEGM_OFFS[order]; return NGSX_RULE_SEGM_OFFS[order + 1] - NGSX_RULE_SEGM_OFFS[order];
+  case 2: if (order > NGSX_RULE_TRIG_MAXORDER) return ORC_UNSUP;
+    *data = NGSX_RULE_TRIG_DATA + NGSX_RULE_TRIG_OFFS[order]; return NGSX_RULE_TRIG_OFFS[order + 1] - NGSX_RULE_TRIG_OFFS[order];
+  case 3: if (order > NGSX_RULE_TET_MAXORDER) return ORC_UNSUP;
+    *data = NGSX_RULE_TET_DATA + NGSX_RULE_TET_OFFS[order]; return NGSX_RULE_TET_OFFS[order + 1] - NGSX_RULE_TET_OFFS[order];
+  }
+  return ORC_UNSUP;
+}
+
+int orc_select_rule(int dim, int order, double *pts3, double *wts, int cap)
+{
+  const double (*d)[4];
+  int n = select_rule(dim, order, &d);
+  if (n < 0) return n;
+  if (n > cap) return ORC_CAP;
+  for (int i = 0; i < n; i++) { pts3[3*i] = d[i][0]; pts3[3*i+1] = d[i][1]; pts3[3*i+2] = d[i][2]; wts[i] = d[i][3]; }
+  return n;
+}
+
+/* ------------------------------------------------------------------ classification */
+/* cutint/straightcutrule.cpp:11-39 CheckIfStraightCut (epsilon = 0) */
+int orc_check_straight_cut(int n, const double *v)
+{
+  int haspos = 0, hasneg = 0;
+  for (int i = 0; i < n; i++) {
+    if (v[i] > 0.0) haspos = 1;
+    if (v[i] < 0.0) hasneg = 1;
+  }
+  if ((hasneg && haspos) || (!hasneg && !haspos)) return IF;
+  return hasneg ? NEG : POS;
+}
+
+/* ------------------------------------------------------------------ cut geometry */
+typedef struct { double p[4][3]; int n; } simplex_t;       /* SimpleX: n points, D = n-1 */
+
+static void ref_simplex(int dim, simplex_t *s)             /* cutint/straightcutrule.hpp:57-62 */
+{
+  memset(s, 0, sizeof *s);
+  s->n = dim + 1;
+  for (int i = 0; i < dim; i++) s->p[i][i] = 1.0;            /* (1,0,0),(0,1,0),(0,0,1),(0,0,0) */
+}
+
+/* cutint/straightcutrule.cpp:41-64 SimpleX::CalcIFPolytopEUsingLset.
+ * returns number of cut points, or ORC_THROW where the reference throws
+ * ("You tried to cut a simplex with a plain geometry lset function"). */
+static int calc_cut_points(const simplex_t *s, const double *ls, double cut[6][3])
+{
+  if (orc_check_straight_cut(s->n, ls) != IF) return ORC_THROW;
+  int D = s->n - 1;
+  if (D == 1) {
+    double f = ls[0] / (ls[0] - ls[1]);
+    for (int d = 0; d < 3; d++) cut[0][d] = s->p[0][d] + f * (s->p[1][d] - s->p[0][d]);
+    return 1;
+  }
+  int nc = 0;
+  for (int i = 0; i < s->n; i++)
+    for (int j = i + 1; j < s->n; j++)
+      if ((ls[i] >= 0) != (ls[j] >= 0)) {
+        double l2[2] = {ls[i], ls[j]};
+        if (orc_check_straight_cut(2, l2) != IF) return ORC_THROW;     /* recursion into the 1-D SimpleX, :45-49 */
+        double f = ls[i] / (ls[i] - ls[j]);
+        for (int d = 0; d < 3; d++) cut[nc][d] = s->p[i][d] + f * (s->p[j][d] - s->p[i][d]);
+        nc++;
+      }
+  return nc;
+}
+
+/* cutint/straightcutrule.cpp:66-72 SimpleX::GetVolume */
+static double simplex_volume(const simplex_t *s)
+{
+  int D = s->n - 1;
+  double a[3], b[3], c[3];
+  if (D == 0) return 1.0;
+  if (D == 1) {
+    for (int d = 0; d < 3; d++) a[d] = s->p[1][d] - s->p[0][d];
+    return sqrt(a[0]*a[0] + a[1]*a[1] + a[2]*a[2]);
+  }
+  if (D == 2) {
+    for (int d = 0; d < 3; d++) { a[d] = s->p[2][d] - s->p[0][d]; b[d] = s->p[1][d] - s->p[0][d]; }
+    double cx = a[1]*b[2] - a[2]*b[1], cy = a[2]*b[0] - a[0]*b[2], cz = a[0]*b[1] - a[1]*b[0];
+    return sqrt(cx*cx + cy*cy + cz*cz);
+  }
+  for (int d = 0; d < 3; d++) { a[d] = s->p[3][d] - s->p[0][d]; b[d] = s->p[2][d] - s->p[0][d]; c[d] = s->p[1][d] - s->p[0][d]; }
+  /* Determinant<3>(col0=a, col1=b, col2=c) */
+  double det = a[0]*(b[1]*c[2] - b[2]*c[1]) - b[0]*(a[1]*c[2] - a[2]*c[1]) + c[0]*(a[1]*b[2] - a[2]*b[1]);
+  return fabs(det);
+}
+
+/* cutint/straightcutrule.cpp:80-100 SimpleX::GetPlainIntegrationRule (appends) */
+static int plain_rule(const simplex_t *s, int order, double *pts3, double *wts, int n0, int cap)
+{
+  const double (*r)[4];
+  int D = s->n - 1;
+  int nr = select_rule(D, order, &r);
+  if (nr < 0) return nr;
+  if (n0 + nr > cap) return ORC_CAP;
+  double fac = simplex_volume(s);
+  for (int q = 0; q < nr; q++) {
+    double ow = 1.0;
+    for (int m = 0; m < D; m++) ow -= r[q][m];
+    double pt[3];
+    for (int d = 0; d < 3; d++) pt[d] = ow * s->p[0][d];
+    for (int m = 0; m < D; m++)
+      for (int d = 0; d < 3; d++) pt[d] += r[q][m] * s->p[m + 1][d];
+    for (int d = 0; d < 3; d++) pts3[3*(n0+q)+d] = pt[d];
+    wts[n0 + q] = r[q][3] * fac;
+  }
+  return n0 + nr;
+}
+
+static void set_pts(simplex_t *s, int n, const double *a, const double *b, const double *c, const double *d)
+{
+  const double *q[4] = {a, b, c, d};
+  s->n = n;
+  for (int i = 0; i < n; i++) memcpy(s->p[i], q[i], 3 * sizeof(double));
+}
+
+/* cutint/straightcutrule.cpp:131-196 LevelsetCutSimplex::Decompose.
+ * returns number of sub-simplices (<=3) or ORC_THROW. */
+static int decompose(int dim, const double *ls, int dt, simplex_t out[3])
+{
+  simplex_t s;
+  ref_simplex(dim, &s);
+  double c[6][3];
+  int nc = calc_cut_points(&s, ls, c);
+  if (nc < 0) return nc;
+  if (dt == IF) {
+    if (nc == dim) {                                 /* s_cut is itself a (D-1)-simplex */
+      out[0].n = nc;
+      for (int i = 0; i < nc; i++) memcpy(out[0].p[i], c[i], sizeof c[i]);
+      return 1;
+    }
+    if (nc == 4 && dim == 3) {
+      set_pts(&out[0], 3, c[0], c[1], c[3], 0);
+      set_pts(&out[1], 3, c[0], c[2], c[3], 0);
+      return 2;
+    }
+    return ORC_THROW;                                 /* "Bad length of s_cut!" */
+  }
+  int rel[4], nrel = 0;
+  for (int i = 0; i < dim + 1; i++)
+    if ((dt == POS && ls[i] >= 0) || (dt == NEG && ls[i] < 0)) rel[nrel++] = i;
+  if (nrel == 1) {                                    /* :156-160 {cuts..., v} */
+    out[0].n = nc + 1;
+    for (int i = 0; i < nc; i++) memcpy(out[0].p[i], c[i], sizeof c[i]);
+    memcpy(out[0].p[nc], s.p[rel[0]], sizeof c[0]);
+    if (out[0].n != dim + 1) return ORC_THROW;
+    return 1;
+  }
+  if (nrel == 2 && dim == 2) {                        /* :161-168 */
+    set_pts(&out[0], 3, s.p[rel[0]], s.p[rel[1]], c[1], 0);
+    set_pts(&out[1], 3, c[0], c[1], s.p[rel[0]], 0);
+    return 2;
+  }
+  if (nrel == 2 && dim == 3) {                        /* :169-178 */
+    set_pts(&out[0], 4, s.p[rel[1]], c[1], c[2], c[3]);
+    set_pts(&out[1], 4, s.p[rel[0]], s.p[rel[1]], c[1], c[2]);
+    set_pts(&out[2], 4, c[0], c[1], c[2], s.p[rel[0]]);
+    return 3;
+  }
+  if (nrel == 3 && dim == 3) {                        /* :179-188 */
+    set_pts(&out[0], 4, c[0], c[1], c[2], s.p[rel[2]]);
+    set_pts(&out[1], 4, s.p[rel[0]], s.p[rel[1]], s.p[rel[2]], c[1]);
+    set_pts(&out[2], 4, c[0], c[1], s.p[rel[0]], s.p[rel[2]]);
+    return 3;
+  }
+  return ORC_THROW;                                   /* "Cutting this part of a tetraeder is not implemented yet!" */
+}
+
+/* cutint/straightcutrule.cpp:663-726 StraightCutIntegrationRuleUntransformed (simplices).
+ * returns npts >= 0, ORC_NULL (-1) for "no rule" (nullptr), ORC_THROW (-2) where the reference throws. */
+int orc_cut_rule_untrafo(int dim, const double *ls, int dt, int order, double *pts3, double *wts, int cap)
+{
+  int dom = orc_check_straight_cut(dim + 1, ls);
+  if (dom != IF) {
+    if (dom != dt) return ORC_NULL;
+    return orc_select_rule(dim, order, pts3, wts, cap);
+  }
+  simplex_t sub[3];
+  int ns = decompose(dim, ls, dt, sub);
+  if (ns < 0) return ns;
+  int n = 0;
+  for (int k = 0; k < ns; k++) {
+    n = plain_rule(&sub[k], order, pts3, wts, n, cap);
+    if (n < 0) return n;
+  }
+  return n;
+}
+
+/* ------------------------------------------------------------------ affine element geometry */
+/* FE_ElementTransformation with the P1 element: x = sum_i lam_i p_i, lam = (xi..., 1-sum xi)
+ * => J[:,k] = p_k - p_dim  (NGS/fem/elementtransformation.hpp:199-220; Appendix B of SURVEY.md) */
+typedef struct { double J[3][3], Jinv[3][3], det, p0[3]; int dim; } affine_t;
+
+static void affine_init(int dim, const double *pmat, affine_t *A)
+{
+  memset(A, 0, sizeof *A);
+  A->dim = dim;
+  for (int r = 0; r < dim; r++) {
+    for (int k = 0; k < dim; k++) A->J[r][k] = pmat[k*dim + r] - pmat[dim*dim + r];
+    A->p0[r] = pmat[dim*dim + r];
+  }
+  double (*J)[3] = A->J, (*I)[3] = A->Jinv;
+  if (dim == 1) { A->det = J[0][0]; I[0][0] = 1.0 / J[0][0]; }
+  else if (dim == 2) {
+    double det = J[0][0]*J[1][1] - J[0][1]*J[1][0];
+    A->det = det;
+    double id = 1.0 / det;
+    I[0][0] = id * J[1][1]; I[0][1] = -id * J[0][1]; I[1][0] = -id * J[1][0]; I[1][1] = id * J[0][0];
+  } else {
+    /* NGS/basiclinalg CalcInverse(Mat<3,3>): cofactors / det */
+    double h0 = J[1][1]*J[2][2] - J[2][1]*J[1][2];
+    double h1 = J[2][1]*J[0][2] - J[0][1]*J[2][2];
+    double h2 = J[0][1]*J[1][2] - J[1][1]*J[0][2];
+    double det = J[0][0]*h0 + J[1][0]*h1 + J[2][0]*h2;
+    A->det = det;
+    double id = 1.0 / det;
+    I[0][0] = id*h0; I[0][1] = id*h1; I[0][2] = id*h2;
+    I[1][0] = id*(J[2][0]*J[1][2] - J[1][0]*J[2][2]);
+    I[1][1] = id*(J[0][0]*J[2][2] - J[2][0]*J[0][2]);
+    I[1][2] = id*(J[1][0]*J[0][2] - J[0][0]*J[1][2]);
+    I[2][0] = id*(J[1][0]*J[2][1] - J[2][0]*J[1][1]);
+    I[2][1] = id*(J[2][0]*J[0][1] - J[0][0]*J[2][1]);
+    I[2][2] = id*(J[0][0]*J[1][1] - J[1][0]*J[0][1]);
+  }
+}
+
+static void affine_map(const affine_t *A, const double *xi, double *x)
+{
+  for (int r = 0; r < 3; r++) x[r] = 0;
+  for (int r = 0; r < A->dim; r++) {
+    double v = A->p0[r];
+    for (int k = 0; k < A->dim; k++) v += A->J[r][k] * xi[k];
+    x[r] = v;
+  }
+}
+
+/* cutint/straightcutrule.cpp:503-537 LevelsetWrapper (simplex part): constant gradient of the P1 level set on the
+ * reference element, normal = grad/|grad| */
+static void lset_ref_normal(int dim, const double *ls, double *n)
+{
+  double g[3] = {0, 0, 0};
+  for (int k = 0; k < dim; k++) g[k] = ls[k] - ls[dim];
+  double nrm = sqrt(g[0]*g[0] + g[1]*g[1] + g[2]*g[2]);
+  for (int k = 0; k < 3; k++) n[k] = g[k] / nrm;
+}
+
+/* cutint/straightcutrule.cpp:580-661 StraightCutIntegrationRule incl. :558-576
+ * TransformQuadUntrafoToIRInterface: IF weights *= | F^-T n_ref |  (caller multiplies by |det F| afterwards) */
+int orc_cut_rule(int dim, const double *pmat, const double *ls, int dt, int order, double *pts3, double *wts, int cap)
+{
+  int n = orc_cut_rule_untrafo(dim, ls, dt, order, pts3, wts, cap);
+  if (n < 0) return n;
+  if (dt == IF && orc_check_straight_cut(dim + 1, ls) == IF) {
+    affine_t A;
+    affine_init(dim, pmat, &A);
+    double nr[3], v[3] = {0, 0, 0};
+    lset_ref_normal(dim, ls, nr);
+    for (int r = 0; r < dim; r++)
+      for (int k = 0; k < dim; k++) v[r] += A.Jinv[k][r] * nr[k];     /* Trans(Finv) * n */
+    double fac = sqrt(v[0]*v[0] + v[1]*v[1] + v[2]*v[2]);
+    for (int i = 0; i < n; i++) wts[i] *= fac;
+  }
+  return n;
+}
+
+/* xfem/cutinfo.cpp:79-111: part volumes from two order-0 rules -> domain type + cut ratio */
+int orc_cutinfo_element(int dim, const double *pmat, const double *ls, double *ratio)
+{
+  double pv[2] = {0, 0}, pts[3*8], w[8];
+  const int order_np[2] = {POS, NEG};
+  for (int k = 0; k < 2; k++) {
+    int np = order_np[k];
+    int n = orc_cut_rule(dim, pmat, ls, np, 0, pts, w, 8);
+    if (n == ORC_THROW) return ORC_THROW;
+    for (int i = 0; i < n; i++) pv[np] += w[i];
+  }
+  *ratio = pv[NEG] / (pv[NEG] + pv[POS]);
+  if (pv[NEG] > 0.0) return pv[POS] > 0.0 ? IF : NEG;
+  return POS;
+}
+
+/* ------------------------------------------------------------------ H1 high-order shapes, orders 1..3 */
+/* NGS/fem/elementtopology.cpp:143-146 (trig edges), :161-167 (tet edges), faces :171-176 */
+static const int TRIG_EDGES[3][2] = {{2,0},{1,2},{0,1}};
+static const int TET_EDGES[6][2] = {{3,0},{3,1},{3,2},{0,1},{0,2},{1,2}};
+static const int TET_FACES[4][3] = {{3,1,2},{3,2,0},{3,0,1},{0,2,1}};
+
+int orc_h1_ndof(int dim, int order)
+{
+  if (dim == 2) return (order + 1) * (order + 2) / 2;
+  if (dim == 3) return (order + 1) * (order + 2) * (order + 3) / 6;
+  return order + 1;
+}
+
+/* NGS/fem/h1hofe_impl.hpp:78-108 (trig), :250-312 (tet); IntLegNoBubble P0=-1/2, P1=-x/2 (NGS/fem/recursive_pol.hpp:1372-1374);
+ * vertex-oriented edge: e[0],e[1] swapped so that vnums[e[0]] > vnums[e[1]]  (NGS/fem/elementtopology.hpp GetVertexOrientedEdge).
+ * shape[ndof], dshape[ndof][dim] w.r.t. reference coordinates. */
+int orc_h1_shape(int dim, int order, const int *vnums, const double *xi, double *shape, double *dshape)
+{
+  if (order < 1 || order > 3 || dim < 2 || dim > 3) return ORC_UNSUP;
+  int nv = dim + 1;
+  double lam[4], dlam[4][3];
+  memset(dlam, 0, sizeof dlam);
+  double s = 0;
+  for (int i = 0; i < dim; i++) { lam[i] = xi[i]; dlam[i][i] = 1.0; s += xi[i]; }
+  lam[dim] = 1.0 - s;
+  for (int d = 0; d < dim; d++) dlam[dim][d] = -1.0;
+  int ii = 0;
+  for (int i = 0; i < nv; i++, ii++) {
+    shape[ii] = lam[i];
+    for (int d = 0; d < dim; d++) dshape[ii*dim + d] = dlam[i][d];
+  }
+  if (order >= 2) {
+    int ne = dim == 2 ? 3 : 6;
+    for (int e = 0; e < ne; e++) {
+      int a = dim == 2 ? TRIG_EDGES[e][0] : TET_EDGES[e][0];
+      int b = dim == 2 ? TRIG_EDGES[e][1] : TET_EDGES[e][1];
+      int va = vnums ? vnums[a] : a, vb = vnums ? vnums[b] : b;
+      if (va > vb) { int t = a; a = b; b = t; }          /* e[0] = vertex with the smaller global number */
+      /* EvalScaledMult(n, x = lam[e1]-lam[e0], t = lam[e0]+lam[e1], c = lam[e0]*lam[e1]):  c*P0, c*P1(x) , ... */
+      double c = lam[a] * lam[b];
+      double x = lam[b] - lam[a];
+      shape[ii] = -0.5 * c;
+      for (int d = 0; d < dim; d++) dshape[ii*dim + d] = -0.5 * (dlam[a][d]*lam[b] + lam[a]*dlam[b][d]);
+      ii++;
+      if (order >= 3) {
+        shape[ii] = -0.5 * x * c;
+        for (int d = 0; d < dim; d++)
+          dshape[ii*dim + d] = -0.5 * ((dlam[b][d] - dlam[a][d]) * c + x * (dlam[a][d]*lam[b] + lam[a]*dlam[b][d]));
+        ii++;
+      }
+    }
+  }
+  if (order >= 3) {
+    int nf = dim == 2 ? 1 : 4;
+    for (int f = 0; f < nf; f++) {
+      int a = dim == 2 ? 0 : TET_FACES[f][0], b = dim == 2 ? 1 : TET_FACES[f][1], c = dim == 2 ? 2 : TET_FACES[f][2];
+      /* DubinerBasis order 0 = 1  times  lam_a lam_b lam_c */
+      shape[ii] = lam[a] * lam[b] * lam[c];
+      for (int d = 0; d < dim; d++)
+        dshape[ii*dim + d] = dlam[a][d]*lam[b]*lam[c] + lam[a]*dlam[b][d]*lam[c] + lam[a]*lam[b]*dlam[c][d];
+      ii++;
+    }
+  }
+  return ii;
+}
+
+/* ------------------------------------------------------------------ element matrix / vector */
+#define ORC_MAXPTS 1024
+#define ORC_MAXND 20
+
+static double eval_mono(int nmono, const double *mono, const double *x)
+{
+  double f = 0;
+  for (int m = 0; m < nmono; m++)
+    f += mono[4*m] * pow(x[0], mono[4*m+1]) * pow(x[1], mono[4*m+2]) * pow(x[2], mono[4*m+3]);
+  return f;
+}
+
+/* xfem/symboliccutbfi.cpp:73-315 T_CalcElementMatrixAdd for  form = c_stiff grad(u).grad(v) + c_mass u v  on an affine simplex:
+ * rule :117, D = coef*measure*w :219-227, elmat += B D B^T :246-301.  elmat is ndof x ndof row-major (rows = test). */
+int orc_elmat_h1(int dim, int fe_order, const int *vnums, const double *pmat, const double *ls, int dt, int intorder,
+                 double c_mass, double c_stiff, double *elmat)
+{
+  static _Thread_local double pts[3*ORC_MAXPTS], w[ORC_MAXPTS];
+  int np = orc_cut_rule(dim, pmat, ls, dt, intorder, pts, w, ORC_MAXPTS);
+  int nd = orc_h1_ndof(dim, fe_order);
+  if (np < 0) return np;
+  affine_t A;
+  affine_init(dim, pmat, &A);
+  double meas = fabs(A.det);
+  for (int i = 0; i < nd*nd; i++) elmat[i] = 0;
+  double shape[ORC_MAXND], dref[ORC_MAXND*3], dphys[ORC_MAXND*3];
+  for (int q = 0; q < np; q++) {
+    if (orc_h1_shape(dim, fe_order, vnums, pts + 3*q, shape, dref) < 0) return ORC_UNSUP;
+    for (int i = 0; i < nd; i++)                     /* dshape_phys = dshape_ref * Finv  (DiffOpGradient) */
+      for (int d = 0; d < dim; d++) {
+        double v = 0;
+        for (int k = 0; k < dim; k++) v += dref[i*dim + k] * A.Jinv[k][d];
+        dphys[i*dim + d] = v;
+      }
+    double fac = meas * w[q];
+    for (int i = 0; i < nd; i++)
+      for (int j = 0; j < nd; j++) {
+        double g = 0;
+        for (int d = 0; d < dim; d++) g += dphys[i*dim + d] * dphys[j*dim + d];
+        elmat[i*nd + j] += fac * (c_stiff * g + c_mass * shape[i] * shape[j]);
+      }
+  }
+  return np;
+}
+
+/* xfem/symboliccutlfi.cpp:52-158 T_CalcElementVector, f = sum_m c_m x^a y^b z^c */
+int orc_elvec_h1(int dim, int fe_order, const int *vnums, const double *pmat, const double *ls, int dt, int intorder,
+                 int nmono, const double *mono, double *elvec)
+{
+  static _Thread_local double pts[3*ORC_MAXPTS], w[ORC_MAXPTS];
+  int np = orc_cut_rule(dim, pmat, ls, dt, intorder, pts, w, ORC_MAXPTS);
+  int nd = orc_h1_ndof(dim, fe_order);
+  if (np < 0) return np;
+  affine_t A;
+  affine_init(dim, pmat, &A);
+  double meas = fabs(A.det);
+  for (int i = 0; i < nd; i++) elvec[i] = 0;
+  double shape[ORC_MAXND], dref[ORC_MAXND*3], x[3];
+  for (int q = 0; q < np; q++) {
+    orc_h1_shape(dim, fe_order, vnums, pts + 3*q, shape, dref);
+    affine_map(&A, pts + 3*q, x);
+    double pv = meas * w[q] * eval_mono(nmono, mono, x);
+    for (int i = 0; i < nd; i++) elvec[i] += pv * shape[i];
+  }
+  return np;
+}
+
+/* ------------------------------------------------------------------ mesh-level loops */
+static void gather_el(int dim, const int32_t *el2v, const double *vert, const double *lset_v, int64_t e, double *pmat, double *ls, int *vn)
+{
+  for (int i = 0; i < dim + 1; i++) {
+    int v = el2v[e*(dim+1) + i];
+    for (int d = 0; d < dim; d++) pmat[i*dim + d] = vert[(int64_t)v*dim + d];
+    ls[i] = lset_v[v];
+    if (vn) vn[i] = v;
+  }
+}
+
+/* utils/p1interpol.cpp:86-90 clamp */
+void orc_interpolate_p1_clamp(int64_t nv, const double *in, double eps, double *out)
+{
+  for (int64_t i = 0; i < nv; i++) { double v = in[i]; if (fabs(v) < eps) v = eps; out[i] = v; }
+}
+
+/* xfem/cutinfo.cpp:54-120 CutInformation::Update, VOL part. dom[e] in {NEG,POS,IF} or -2 where the reference throws. returns #throws */
+int64_t orc_cutinfo_mesh(int dim, int64_t ne, const int32_t *el2v, const double *vert, const double *lset_v,
+                         int8_t *dom, double *ratio)
+{
+  int64_t nerr = 0;
+#pragma omp parallel for schedule(static) reduction(+:nerr)
+  for (int64_t e = 0; e < ne; e++) {
+    double pmat[12], ls[4];
+    gather_el(dim, el2v, vert, lset_v, e, pmat, ls, 0);
+    int r = orc_cutinfo_element(dim, pmat, ls, &ratio[e]);
+    dom[e] = (int8_t)r;
+    if (r < 0) nerr++;
+  }
+  return nerr;
+}
+
+/* per element rule sizes for (dt, order): -1 = no rule. */
+void orc_rule_count_mesh(int dim, int64_t ne, const int32_t *el2v, const double *lset_v, int dt, int order, int32_t *npts)
+{
+#pragma omp parallel for schedule(static)
+  for (int64_t e = 0; e < ne; e++) {
+    static _Thread_local double pts[3*ORC_MAXPTS], w[ORC_MAXPTS];
+    double ls[4];
+    for (int i = 0; i < dim + 1; i++) ls[i] = lset_v[el2v[e*(dim+1) + i]];
+    npts[e] = orc_cut_rule_untrafo(dim, ls, dt, order, pts, w, ORC_MAXPTS);
+  }
+}
+
+/* cutint/python_cutint.cpp:41-68 IntegrateX, cf = polynomial; per-element partials summed in element order (the reference's
+ * AtomicAdd order is thread-dependent; any order is "the reference" up to re-association). */
+double orc_integrate_mesh(int dim, int64_t ne, const int32_t *el2v, const double *vert, const double *lset_v, int dt, int order,
+                          int nmono, const double *mono, int64_t *npts_total)
+{
+  double sum = 0;
+  int64_t nptot = 0;
+#pragma omp parallel for schedule(static) reduction(+:sum,nptot)
+  for (int64_t e = 0; e < ne; e++) {
+    static _Thread_local double pts[3*ORC_MAXPTS], w[ORC_MAXPTS];
+    double pmat[12], ls[4], x[3];
+    gather_el(dim, el2v, vert, lset_v, e, pmat, ls, 0);
+    int np = orc_cut_rule(dim, pmat, ls, dt, order, pts, w, ORC_MAXPTS);
+    if (np < 0) continue;
+    affine_t A;
+    affine_init(dim, pmat, &A);
+    double meas = fabs(A.det), lsum = 0;
+    for (int q = 0; q < np; q++) {
+      affine_map(&A, pts + 3*q, x);
+      lsum += meas * w[q] * eval_mono(nmono, mono, x);
+    }
+    sum += lsum;
+    nptot += np;
+  }
+  if (npts_total) *npts_total = nptot;
+  return sum;
+}
+
+/* batched element matrices (els == NULL: all elements) */
+int64_t orc_elmat_mesh(int dim, int64_t nel, const int64_t *els, const int32_t *el2v, const double *vert, const double *lset_v,
+                       int fe_order, int dt, int intorder, double c_mass, double c_stiff, double *elmats, int32_t *npts)
+{
+  int nd = orc_h1_ndof(dim, fe_order);
+  int64_t nn = 0;
+#pragma omp parallel for schedule(dynamic,256) reduction(+:nn)
+  for (int64_t k = 0; k < nel; k++) {
+    int64_t e = els ? els[k] : k;
+    double pmat[12], ls[4];
+    int vn[4];
+    gather_el(dim, el2v, vert, lset_v, e, pmat, ls, vn);
+    int r = orc_elmat_h1(dim, fe_order, vn, pmat, ls, dt, intorder, c_mass, c_stiff, elmats + (size_t)k*nd*nd);
+    if (npts) npts[k] = r;
+    if (r < 0) memset(elmats + (size_t)k*nd*nd, 0, sizeof(double)*nd*nd); else nn++;
+  }
+  return nn;
+}
+
+/* NGS/comp/bilinearform.cpp:1117-1563 element loop (colour by colour, NGS/comp/fespace.cpp:1540-1566) +
+ * NGS/linalg/sparsematrix_impl.hpp:63-103 SparseMatrixTM::AddElementMatrix (sorted columns, linear scan of the row). */
+int64_t orc_assemble_csr(int dim, const int32_t *el2v, const double *vert, const double *lset_v,
+                         int fe_order, const int32_t *el2dof, int dt, int intorder, double c_mass, double c_stiff,
+                         int ncolors, const int64_t *color_ptr, const int32_t *color_els,
+                         const int64_t *rowptr, const int32_t *colidx, double *vals)
+{
+  int nd = orc_h1_ndof(dim, fe_order);
+  int64_t nass = 0;
+  for (int c = 0; c < ncolors; c++) {
+#pragma omp parallel for schedule(dynamic,64) reduction(+:nass)
+    for (int64_t k = color_ptr[c]; k < color_ptr[c+1]; k++) {
+      int64_t e = color_els[k];
+      double pmat[12], ls[4], elmat[ORC_MAXND*ORC_MAXND];
+      int vn[4];
+      gather_el(dim, el2v, vert, lset_v, e, pmat, ls, vn);
+      int r = orc_elmat_h1(dim, fe_order, vn, pmat, ls, dt, intorder, c_mass, c_stiff, elmat);
+      if (r < 0) continue;
+      nass++;
+      const int32_t *dn = el2dof + e*nd;
+      int map[ORC_MAXND];
+      for (int i = 0; i < nd; i++) map[i] = i;
+      for (int i = 1; i < nd; i++) {                  /* QuickSortI(dnums2, map) */
+        int m = map[i], j = i;
+        while (j > 0 && dn[map[j-1]] > dn[m]) { map[j] = map[j-1]; j--; }
+        map[j] = m;
+      }
+      for (int i = 0; i < nd; i++) {
+        int64_t k0 = rowptr[dn[i]];
+        for (int j1 = 0; j1 < nd; j1++) {
+          int j = map[j1];
+          while (colidx[k0] != dn[j]) k0++;
+          vals[k0] += elmat[i*nd + j];
+        }
+      }
+    }
+  }
+  return nass;
+}
+
+/* NGS/comp/linearform.cpp:209-243 + symboliccutlfi: vec[dof] += elvec (serial, element order) */
+int64_t orc_assemble_vec(int dim, int64_t ne, const int32_t *el2v, const double *vert, const double *lset_v,
+                         int fe_order, const int32_t *el2dof, int dt, int intorder, int nmono, const double *mono, double *vec)
+{
+  int nd = orc_h1_ndof(dim, fe_order);
+  int64_t nass = 0;
+  for (int64_t e = 0; e < ne; e++) {
+    double pmat[12], ls[4], elvec[ORC_MAXND];
+    int vn[4];
+    gather_el(dim, el2v, vert, lset_v, e, pmat, ls, vn);
+    int r = orc_elvec_h1(dim, fe_order, vn, pmat, ls, dt, intorder, nmono, mono, elvec);
+    if (r < 0) continue;
+    nass++;
+    for (int i = 0; i < nd; i++) vec[el2dof[e*nd + i]] += elvec[i];
+  }
+  return nass;
+}
+
+/* xfem/cutinfo.cpp:191-255 GetFacetsWithNeighborTypes (no periodic identification).  facet2el[f][2], -1 = no neighbour.
+ * a,b,out are byte masks (0/1) here; the product packs them as NGSolve BitArray words. */
+void orc_facets_neighbor_types(int64_t nf, const int32_t *facet2el, const uint8_t *a, const uint8_t *b,
+                               int bnd_a, int bnd_b, int use_and, uint8_t *out)
+{
+  for (int64_t f = 0; f < nf; f++) {
+    int e0 = facet2el[2*f], e1 = facet2el[2*f + 1];
+    out[f] = 0;
+    if (e0 < 0) continue;
+    int al = a[e0], ar = e1 >= 0 ? a[e1] : bnd_a;
+    int bl = b[e0], br = e1 >= 0 ? b[e1] : bnd_b;
+    if (use_and) out[f] = (al && br) || (ar && bl);
+    else out[f] = (al || br) || (ar || bl);
+  }
+}
+
+/* xfem/cutinfo.cpp:257-279 */
+void orc_elements_with_neighbor_facets(int64_t nf, int64_t ne, const int32_t *facet2el, const uint8_t *a, uint8_t *out)
+{
+  memset(out, 0, ne);
+  for (int64_t f = 0; f < nf; f++)
+    if (a[f]) for (int k = 0; k < 2; k++) if (facet2el[2*f + k] >= 0) out[facet2el[2*f + k]] = 1;
+}
+
+/* xfem/cutinfo.cpp:281-304 */
+void orc_dofs_of_elements(int64_t ne, int nd, int64_t ndof, const int32_t *el2dof, const uint8_t *a, uint8_t *out)
+{
+  memset(out, 0, ndof);
+  for (int64_t e = 0; e < ne; e++)
+    if (a[e]) for (int i = 0; i < nd; i++) out[el2dof[e*nd + i]] = 1;
+}
+
+/* xfem/symboliccutbfi.cpp:1202-1411 SymbolicFacetPatchBilinearFormIntegrator::CalcFacetMatrix for the ghost-penalty form
+ *   c * (u - u.Other()) * (v - v.Other())       (py_tutorials/fictdom_ghostpen.py:105-107)
+ * on affine simplices: volume rules of order 2*fe_order on BOTH elements (:1219-1220); each point is pulled back into
+ * the other element (MapPatchIntegrationPoint :1115-1199 -- exact in one step for affine maps); weight mir.GetWeight().
+ * elmat is (2 nd)x(2 nd) row-major over [dofs of el1 | dofs of el2]. */
+int orc_facetpatch_elmat_h1(int dim, int fe_order, const int *vn1, const double *pmat1, const int *vn2, const double *pmat2,
+                            double coef, double *elmat)
+{
+  int nd = orc_h1_ndof(dim, fe_order), n2 = 2*nd;
+  const double (*r)[4];
+  int nr = select_rule(dim, 2*fe_order, &r);
+  if (nr < 0) return nr;
+  affine_t A[2];
+  affine_init(dim, pmat1, &A[0]);
+  affine_init(dim, pmat2, &A[1]);
+  for (int i = 0; i < n2*n2; i++) elmat[i] = 0;
+  double sh[2][ORC_MAXND], dref[ORC_MAXND*3], jump[2*ORC_MAXND];
+  for (int side = 0; side < 2; side++) {
+    const affine_t *Ah = &A[side], *Ao = &A[1-side];
+    const int *vh = side == 0 ? vn1 : vn2, *vo = side == 0 ? vn2 : vn1;
+    double meas = fabs(Ah->det);
+    for (int q = 0; q < nr; q++) {
+      double xi[3] = {r[q][0], r[q][1], r[q][2]}, x[3], xo[3] = {0, 0, 0};
+      affine_map(Ah, xi, x);
+      for (int k = 0; k < dim; k++) {                  /* xo = Finv_other (x - p0_other) */
+        double v = 0;
+        for (int rr = 0; rr < dim; rr++) v += Ao->Jinv[k][rr] * (x[rr] - Ao->p0[rr]);
+        xo[k] = v;
+      }
+      orc_h1_shape(dim, fe_order, vh, xi, sh[0], dref);
+      orc_h1_shape(dim, fe_order, vo, xo, sh[1], dref);
+      /* u - u.Other(): +shape on the element owning the point, -shape (extended polynomial) on the other */
+      for (int i = 0; i < nd; i++) {
+        jump[(side == 0 ? 0 : nd) + i] = sh[0][i];
+        jump[(side == 0 ? nd : 0) + i] = -sh[1][i];
+      }
+      double fac = coef * meas * r[q][3];
+      for (int i = 0; i < n2; i++)
+        for (int j = 0; j < n2; j++) elmat[i*n2 + j] += fac * jump[i] * jump[j];
+    }
+  }
+  return 2*nr;
+}
+
+int orc_max_threads(void)
+{
+#ifdef _OPENMP
+  return omp_get_max_threads();
+#else
+  return 1;
+#endif
+}
+void orc_set_threads(int n)
+{
+#ifdef _OPENMP
+  if (n > 0) omp_set_num_threads(n);
+#else
+  (void)n;
+#endif
+}

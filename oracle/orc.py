@@ -1,0 +1,277 @@
+"""TEST INFRASTRUCTURE -- numpy front-end to the CPU oracle (oracle/libngsx_oracle.so, plain-C
+restatement in oracle/ngsx_oracle.c) and to the compiled reference (oracle/_ref, via refload).
+Not part of the product path: only tests/, __graft_entry__.smoke() and bench.py's CPU legs import it."""
+import ctypes
+import os
+import subprocess
+
+import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+_LIB = None
+NEG, POS, IF = 0, 1, 2
+ET = {1: 1, 2: 10, 3: 20}   # dim -> NGSolve ELEMENT_TYPE (NGS/fem/elementtopology.hpp:22-25)
+
+c_int, c_i64, c_double = ctypes.c_int, ctypes.c_int64, ctypes.c_double
+dp = ctypes.POINTER(ctypes.c_double)
+ip = ctypes.POINTER(ctypes.c_int32)
+lp = ctypes.POINTER(ctypes.c_int64)
+bp = ctypes.POINTER(ctypes.c_int8)
+ubp = ctypes.POINTER(ctypes.c_uint8)
+
+
+def lib_path():
+    return os.path.join(_HERE, "libngsx_oracle.so")
+
+
+def build(force=False):
+    if force or not os.path.exists(lib_path()) or \
+            os.path.getmtime(lib_path()) < os.path.getmtime(os.path.join(_HERE, "ngsx_oracle.c")):
+        subprocess.check_call(["make", "-C", _HERE, "libngsx_oracle.so"], stdout=subprocess.DEVNULL)
+
+
+def load():
+    global _LIB
+    if _LIB is not None:
+        return _LIB
+    build()
+    L = ctypes.CDLL(lib_path())
+    L.orc_select_rule.argtypes = [c_int, c_int, dp, dp, c_int]
+    L.orc_check_straight_cut.argtypes = [c_int, dp]
+    L.orc_cut_rule_untrafo.argtypes = [c_int, dp, c_int, c_int, dp, dp, c_int]
+    L.orc_cut_rule.argtypes = [c_int, dp, dp, c_int, c_int, dp, dp, c_int]
+    L.orc_cutinfo_element.argtypes = [c_int, dp, dp, dp]
+    L.orc_h1_ndof.argtypes = [c_int, c_int]
+    L.orc_h1_shape.argtypes = [c_int, c_int, ip, dp, dp, dp]
+    L.orc_elmat_h1.argtypes = [c_int, c_int, ip, dp, dp, c_int, c_int, c_double, c_double, dp]
+    L.orc_elvec_h1.argtypes = [c_int, c_int, ip, dp, dp, c_int, c_int, c_int, dp, dp]
+    L.orc_interpolate_p1_clamp.argtypes = [c_i64, dp, c_double, dp]
+    L.orc_cutinfo_mesh.argtypes = [c_int, c_i64, ip, dp, dp, bp, dp]
+    L.orc_cutinfo_mesh.restype = c_i64
+    L.orc_rule_count_mesh.argtypes = [c_int, c_i64, ip, dp, c_int, c_int, ip]
+    L.orc_integrate_mesh.argtypes = [c_int, c_i64, ip, dp, dp, c_int, c_int, c_int, dp, lp]
+    L.orc_integrate_mesh.restype = c_double
+    L.orc_elmat_mesh.argtypes = [c_int, c_i64, lp, ip, dp, dp, c_int, c_int, c_int, c_double, c_double, dp, ip]
+    L.orc_elmat_mesh.restype = c_i64
+    L.orc_assemble_csr.argtypes = [c_int, ip, dp, dp, c_int, ip, c_int, c_int, c_double, c_double,
+                                   c_int, lp, ip, lp, ip, dp]
+    L.orc_assemble_csr.restype = c_i64
+    L.orc_assemble_vec.argtypes = [c_int, c_i64, ip, dp, dp, c_int, ip, c_int, c_int, c_int, dp, dp]
+    L.orc_assemble_vec.restype = c_i64
+    L.orc_facets_neighbor_types.argtypes = [c_i64, ip, ubp, ubp, c_int, c_int, c_int, ubp]
+    L.orc_elements_with_neighbor_facets.argtypes = [c_i64, c_i64, ip, ubp, ubp]
+    L.orc_dofs_of_elements.argtypes = [c_i64, c_int, c_i64, ip, ubp, ubp]
+    L.orc_facetpatch_elmat_h1.argtypes = [c_int, c_int, ip, dp, ip, dp, c_double, dp]
+    L.orc_set_threads.argtypes = [c_int]
+    _LIB = L
+    return L
+
+
+def _d(a):
+    return np.ascontiguousarray(a, dtype=np.float64)
+
+
+def _i(a):
+    return np.ascontiguousarray(a, dtype=np.int32)
+
+
+def P(a, t=dp):
+    return a.ctypes.data_as(t)
+
+
+def mono_array(mono):
+    """integrand sum_m c * x^a y^b z^c  given as list of (c, a, b, c); None -> constant 1"""
+    if mono is None:
+        mono = [(1.0, 0, 0, 0)]
+    return _d(np.array(mono, dtype=np.float64).reshape(-1, 4))
+
+
+# ----------------------------------------------------------------------------- single-element wrappers
+def cut_rule_untrafo(dim, lset, dt, order, impl="oracle", cap=2048):
+    pts = np.zeros((cap, 3)); w = np.zeros(cap)
+    ls = _d(lset)
+    if impl == "oracle":
+        n = load().orc_cut_rule_untrafo(dim, P(ls), dt, order, P(pts), P(w), cap)
+    else:
+        from . import refload
+        n = refload.load().ref_cut_rule_untrafo(ET[dim], P(ls), dt, order, P(pts), P(w), cap)
+    if n < 0:
+        return n, None, None
+    return n, pts[:n].copy(), w[:n].copy()
+
+
+def cut_rule(dim, pmat, lset, dt, order, impl="oracle", cap=2048):
+    pts = np.zeros((cap, 3)); w = np.zeros(cap)
+    ls = _d(lset); pm = _d(pmat)
+    if impl == "oracle":
+        n = load().orc_cut_rule(dim, P(pm), P(ls), dt, order, P(pts), P(w), cap)
+    else:
+        from . import refload
+        n = refload.load().ref_cut_rule(ET[dim], P(pm), P(ls), dt, order, P(pts), P(w), cap)
+    if n < 0:
+        return n, None, None
+    return n, pts[:n].copy(), w[:n].copy()
+
+
+def cutinfo_element(dim, pmat, lset, impl="oracle"):
+    r = c_double(0)
+    ls = _d(lset); pm = _d(pmat)
+    if impl == "oracle":
+        d = load().orc_cutinfo_element(dim, P(pm), P(ls), ctypes.byref(r))
+    else:
+        from . import refload
+        d = refload.load().ref_cutinfo_element(ET[dim], P(pm), P(ls), ctypes.byref(r))
+    return d, r.value
+
+
+def h1_shape(dim, order, vnums, xi, impl="oracle"):
+    nd = load().orc_h1_ndof(dim, order)
+    sh = np.zeros(nd); dsh = np.zeros((nd, dim))
+    x3 = np.zeros(3); x3[:len(xi)] = xi
+    vn = _i(vnums) if vnums is not None else None
+    vp = P(vn, ip) if vn is not None else None
+    if impl == "oracle":
+        n = load().orc_h1_shape(dim, order, vp, P(x3), P(sh), P(dsh))
+    else:
+        from . import refload
+        n = refload.load().ref_h1_shape(ET[dim], order, vp, P(x3), P(sh), P(dsh))
+    assert n == nd, (n, nd)
+    return sh, dsh
+
+
+def elmat_h1(dim, fe_order, vnums, pmat, lset, dt, intorder, c_mass, c_stiff, impl="oracle"):
+    nd = load().orc_h1_ndof(dim, fe_order)
+    em = np.zeros((nd, nd))
+    vn = _i(vnums); pm = _d(pmat); ls = _d(lset)
+    if impl == "oracle":
+        n = load().orc_elmat_h1(dim, fe_order, P(vn, ip), P(pm), P(ls), dt, intorder, c_mass, c_stiff, P(em))
+    else:
+        from . import refload
+        n = refload.load().ref_elmat_h1(ET[dim], fe_order, P(vn, ip), P(pm), P(ls), dt, intorder, c_mass, c_stiff, P(em))
+    return n, em
+
+
+def elvec_h1(dim, fe_order, vnums, pmat, lset, dt, intorder, mono, impl="oracle"):
+    nd = load().orc_h1_ndof(dim, fe_order)
+    ev = np.zeros(nd)
+    vn = _i(vnums); pm = _d(pmat); ls = _d(lset); mo = mono_array(mono)
+    if impl == "oracle":
+        n = load().orc_elvec_h1(dim, fe_order, P(vn, ip), P(pm), P(ls), dt, intorder, len(mo), P(mo), P(ev))
+    else:
+        from . import refload
+        n = refload.load().ref_elvec_h1(ET[dim], fe_order, P(vn, ip), P(pm), P(ls), dt, intorder, len(mo), P(mo), P(ev))
+    return n, ev
+
+
+def facetpatch_elmat_h1(dim, fe_order, vn1, pmat1, vn2, pmat2, coef):
+    nd = load().orc_h1_ndof(dim, fe_order)
+    em = np.zeros((2 * nd, 2 * nd))
+    a, b, p1, p2 = _i(vn1), _i(vn2), _d(pmat1), _d(pmat2)
+    n = load().orc_facetpatch_elmat_h1(dim, fe_order, P(a, ip), P(p1), P(b, ip), P(p2), coef, P(em))
+    return n, em
+
+
+# ----------------------------------------------------------------------------- mesh-level wrappers
+def cutinfo_mesh(dim, el2v, vert, lset_v, impl="oracle", nthreads=0):
+    el2v = _i(el2v); vert = _d(vert); lset_v = _d(lset_v)
+    ne = el2v.shape[0]
+    dom = np.zeros(ne, dtype=np.int8); ratio = np.zeros(ne)
+    if impl == "oracle":
+        load().orc_set_threads(nthreads)
+        nerr = load().orc_cutinfo_mesh(dim, ne, P(el2v, ip), P(vert), P(lset_v), P(dom, bp), P(ratio))
+    else:
+        from . import refload
+        nerr = refload.load().ref_cutinfo_mesh(dim, ne, P(el2v, ip), P(vert), P(lset_v),
+                                               dom.ctypes.data_as(ctypes.POINTER(ctypes.c_byte)), P(ratio), nthreads)
+    return dom, ratio, nerr
+
+
+def rule_count_mesh(dim, el2v, lset_v, dt, order):
+    el2v = _i(el2v); lset_v = _d(lset_v)
+    npts = np.zeros(el2v.shape[0], dtype=np.int32)
+    load().orc_rule_count_mesh(dim, el2v.shape[0], P(el2v, ip), P(lset_v), dt, order, P(npts, ip))
+    return npts
+
+
+def integrate_mesh(dim, el2v, vert, lset_v, dt, order, mono=None, impl="oracle", nthreads=0):
+    el2v = _i(el2v); vert = _d(vert); lset_v = _d(lset_v); mo = mono_array(mono)
+    npt = c_i64(0)
+    if impl == "oracle":
+        load().orc_set_threads(nthreads)
+        v = load().orc_integrate_mesh(dim, el2v.shape[0], P(el2v, ip), P(vert), P(lset_v), dt, order, len(mo), P(mo),
+                                      ctypes.byref(npt))
+    else:
+        from . import refload
+        npl = ctypes.c_long(0)
+        v = refload.load().ref_integrate_mesh(dim, el2v.shape[0], P(el2v, ip), P(vert), P(lset_v), dt, order, len(mo), P(mo),
+                                              nthreads, ctypes.byref(npl))
+        npt = c_i64(npl.value)
+    return v, npt.value
+
+
+def elmat_mesh(dim, el2v, vert, lset_v, fe_order, dt, intorder, c_mass, c_stiff, els=None, impl="oracle", nthreads=0):
+    el2v = _i(el2v); vert = _d(vert); lset_v = _d(lset_v)
+    nd = load().orc_h1_ndof(dim, fe_order)
+    if els is not None:
+        els = np.ascontiguousarray(els, dtype=np.int64)
+    nel = el2v.shape[0] if els is None else len(els)
+    em = np.zeros((nel, nd, nd)); npts = np.zeros(nel, dtype=np.int32)
+    elp = P(els, lp) if els is not None else None
+    if impl == "oracle":
+        load().orc_set_threads(nthreads)
+        load().orc_elmat_mesh(dim, nel, elp, P(el2v, ip), P(vert), P(lset_v), fe_order, dt, intorder, c_mass, c_stiff,
+                              P(em), P(npts, ip))
+    else:
+        from . import refload
+        elp = els.ctypes.data_as(ctypes.POINTER(ctypes.c_long)) if els is not None else None
+        refload.load().ref_elmat_mesh(dim, nel, elp, P(el2v, ip), P(vert), P(lset_v), fe_order, dt, intorder, c_mass, c_stiff,
+                                      P(em), P(npts, ip), nthreads)
+    return em, npts
+
+
+def assemble_csr(dim, el2v, vert, lset_v, fe_order, el2dof, dt, intorder, c_mass, c_stiff,
+                 color_ptr, color_els, rowptr, colidx, impl="oracle", nthreads=0):
+    el2v = _i(el2v); vert = _d(vert); lset_v = _d(lset_v); el2dof = _i(el2dof)
+    color_ptr = np.ascontiguousarray(color_ptr, dtype=np.int64); color_els = _i(color_els)
+    rowptr = np.ascontiguousarray(rowptr, dtype=np.int64); colidx = _i(colidx)
+    vals = np.zeros(len(colidx))
+    if impl == "oracle":
+        load().orc_set_threads(nthreads)
+        n = load().orc_assemble_csr(dim, P(el2v, ip), P(vert), P(lset_v), fe_order, P(el2dof, ip), dt, intorder, c_mass, c_stiff,
+                                    len(color_ptr) - 1, P(color_ptr, lp), P(color_els, ip), P(rowptr, lp), P(colidx, ip), P(vals))
+    else:
+        from . import refload
+        clp = ctypes.POINTER(ctypes.c_long)
+        n = refload.load().ref_assemble_csr(dim, P(el2v, ip), P(vert), P(lset_v), fe_order, P(el2dof, ip), dt, intorder,
+                                            c_mass, c_stiff, len(color_ptr) - 1, color_ptr.ctypes.data_as(clp), P(color_els, ip),
+                                            rowptr.ctypes.data_as(clp), P(colidx, ip), P(vals), nthreads)
+    return vals, n
+
+
+def assemble_vec(dim, el2v, vert, lset_v, fe_order, el2dof, ndof, dt, intorder, mono):
+    el2v = _i(el2v); vert = _d(vert); lset_v = _d(lset_v); el2dof = _i(el2dof); mo = mono_array(mono)
+    vec = np.zeros(ndof)
+    load().orc_assemble_vec(dim, el2v.shape[0], P(el2v, ip), P(vert), P(lset_v), fe_order, P(el2dof, ip), dt, intorder,
+                            len(mo), P(mo), P(vec))
+    return vec
+
+
+def facets_neighbor_types(facet2el, a, b, bnd_a=True, bnd_b=True, use_and=True):
+    f2e = _i(facet2el); a = np.ascontiguousarray(a, dtype=np.uint8); b = np.ascontiguousarray(b, dtype=np.uint8)
+    out = np.zeros(f2e.shape[0], dtype=np.uint8)
+    load().orc_facets_neighbor_types(f2e.shape[0], P(f2e, ip), P(a, ubp), P(b, ubp), int(bnd_a), int(bnd_b), int(use_and), P(out, ubp))
+    return out.astype(bool)
+
+
+def elements_with_neighbor_facets(facet2el, ne, a):
+    f2e = _i(facet2el); a = np.ascontiguousarray(a, dtype=np.uint8)
+    out = np.zeros(ne, dtype=np.uint8)
+    load().orc_elements_with_neighbor_facets(f2e.shape[0], ne, P(f2e, ip), P(a, ubp), P(out, ubp))
+    return out.astype(bool)
+
+
+def dofs_of_elements(el2dof, ndof, a):
+    e2d = _i(el2dof); a = np.ascontiguousarray(a, dtype=np.uint8)
+    out = np.zeros(ndof, dtype=np.uint8)
+    load().orc_dofs_of_elements(e2d.shape[0], e2d.shape[1], ndof, P(e2d, ip), P(a, ubp), P(out, ubp))
+    return out.astype(bool)

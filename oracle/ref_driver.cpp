@@ -1,0 +1,399 @@
+// TEST INFRASTRUCTURE -- not part of the product path.
+//
+// extern "C" driver around the reference's OWN compiled sources (ngsxfem
+// cutint/straightcutrule.cpp + NGSolve fem/bla, compiled in place from
+// /root/reference by oracle/build_ref.sh into oracle/_ref/libngsxref.so).
+// Everything numerically relevant below is a call INTO reference code:
+//   * xintegration::StraightCutIntegrationRule[Untransformed]   (cutint/straightcutrule.cpp:580-726)
+//   * ngfem::SelectIntegrationRule                              (NGS/fem/intrule.cpp:2620-2659)
+//   * ngfem::H1HighOrderFE<ET>::CalcShape / CalcMappedDShape    (NGS/fem/h1hofe_impl.hpp)
+//   * ngfem::FE_ElementTransformation / MappedIntegrationRule   (NGS/fem/elementtransformation.cpp)
+//   * ngbla::AddABt                                             (NGS/basiclinalg/ngblas.cpp)
+// The only restated logic is the ~30-line B*D*B^T accumulation of
+// xfem/symboliccutbfi.cpp:219-301 (diagonal-proxy branch; the symbolic
+// CoefficientFunction tree of the reference cannot be built without the full
+// NGSolve comp layer) and the CutInformation::Update decision of
+// xfem/cutinfo.cpp:79-111.
+#include <fem.hpp>
+#include "../cutint/straightcutrule.hpp"
+#include <omp.h>
+
+using namespace ngfem;
+using namespace xintegration;
+
+namespace {
+
+thread_local LocalHeap * tl_lh = nullptr;
+LocalHeap & GetLH()
+{
+  if (!tl_lh) tl_lh = new LocalHeap(8000000, "ref_driver", true);
+  return *tl_lh;
+}
+
+
+int NV(ELEMENT_TYPE et) { return ngfem::Dim(et) + 1; }
+
+int CopyRule(const IntegrationRule * ir, double * pts3, double * wts, int cap)
+{
+  if (!ir) return -1;
+  int n = ir->Size();
+  if (n > cap) return -3;
+  for (int i = 0; i < n; i++)
+    {
+      for (int d = 0; d < 3; d++) pts3[3*i+d] = (*ir)[i](d);
+      wts[i] = (*ir)[i].Weight();
+    }
+  return n;
+}
+
+template <int D>
+const IntegrationRule * TrafoRule(ELEMENT_TYPE et, const double * pmat, const double * lset, int dt, int order, LocalHeap & lh,
+                                  FE_ElementTransformation<D,D> *& trafo_out)
+{
+  Matrix<> pm(D+1, D);
+  for (int i = 0; i < D+1; i++) for (int d = 0; d < D; d++) pm(i,d) = pmat[i*D+d];
+  auto trafo = new (lh) FE_ElementTransformation<D,D>(et, pm);
+  trafo_out = trafo;
+  Vector<> lv(D+1);
+  for (int i = 0; i < D+1; i++) lv(i) = lset[i];
+  return StraightCutIntegrationRule(lv, *trafo, DOMAIN_TYPE(dt), order, FIND_OPTIMAL, lh);
+}
+
+template <ELEMENT_TYPE ET>
+struct ElmatWork
+{
+  enum { D = ET_trait<ET>::DIM };
+
+  // returns npts (>=0), -1 if the reference returns no rule (nullptr), -2 on a reference exception
+  static int Elmat(int fe_order, const int * vnums, const double * pmat, const double * lset, int dt, int intorder,
+                   double c_mass, double c_stiff, double * elmat_out, LocalHeap & lh)
+  {
+    HeapReset hr(lh);
+    H1HighOrderFE<ET> fel(fe_order);
+    if (vnums) for (int i = 0; i < D+1; i++) fel.SetVertexNumber(i, vnums[i]);
+    int nd = fel.GetNDof();
+    FE_ElementTransformation<D,D> * trafo;
+    const IntegrationRule * ir = TrafoRule<D>(ET, pmat, lset, dt, intorder, lh, trafo);
+    if (!ir) return -1;
+    int np = ir->Size();
+    MappedIntegrationRule<D,D> mir(*ir, *trafo, lh);
+    FlatMatrix<> elmat(nd, nd, lh); elmat = 0.0;
+    // symboliccutbfi.cpp:219-227: D = cf-value * measure * weight-from-cut-rule
+    // :246-301: blocks of BS=16 points, bbmat (ndof x bs*dim), bdbmat = bbmat*diag(D), elmat += bbmat*bdbmat^T (AddABt)
+    constexpr int BS = 16;
+    for (int pass = 0; pass < 2; pass++)   // proxy pairs: (grad u, grad v) then (u, v), as SymbolicBFI orders them for grad(u)*grad(v)+u*v
+      {
+        double coef = pass == 0 ? c_stiff : c_mass;
+        if (coef == 0.0) continue;
+        int pd = pass == 0 ? D : 1;
+        for (int i0 = 0; i0 < np; i0 += BS)
+          {
+            HeapReset hr2(lh);
+            int bs = min2(BS, np - i0);
+            FlatMatrix<> bbmat(nd, bs*pd, lh), bdbmat(nd, bs*pd, lh);
+            for (int j = 0; j < bs; j++)
+              {
+                int ii = i0 + j;
+                double dval = coef * mir[ii].GetMeasure() * (*ir)[ii].Weight();
+                if (pass == 0)
+                  {
+                    FlatMatrixFixWidth<D> dshape(nd, lh);
+                    fel.CalcMappedDShape(mir[ii], dshape);
+                    for (int k = 0; k < nd; k++) for (int d = 0; d < D; d++)
+                      { bbmat(k, j*D+d) = dshape(k,d); bdbmat(k, j*D+d) = dval * dshape(k,d); }
+                  }
+                else
+                  {
+                    FlatVector<> shape(nd, lh);
+                    fel.CalcShape((*ir)[ii], shape);
+                    for (int k = 0; k < nd; k++) { bbmat(k, j) = shape(k); bdbmat(k, j) = dval * shape(k); }
+                  }
+              }
+            AddABt(bbmat, bdbmat, elmat);
+          }
+      }
+    for (int i = 0; i < nd; i++) for (int j = 0; j < nd; j++) elmat_out[i*nd+j] = elmat(i,j);
+    return np;
+  }
+
+  // symboliccutlfi.cpp:85-153 with f = sum_m coef_m x^a y^b z^c (polynomial source), intorder passed by caller
+  static int Elvec(int fe_order, const int * vnums, const double * pmat, const double * lset, int dt, int intorder,
+                   int nmono, const double * mono, double * elvec_out, LocalHeap & lh)
+  {
+    HeapReset hr(lh);
+    H1HighOrderFE<ET> fel(fe_order);
+    if (vnums) for (int i = 0; i < D+1; i++) fel.SetVertexNumber(i, vnums[i]);
+    int nd = fel.GetNDof();
+    FE_ElementTransformation<D,D> * trafo;
+    const IntegrationRule * ir = TrafoRule<D>(ET, pmat, lset, dt, intorder, lh, trafo);
+    if (!ir) return -1;
+    int np = ir->Size();
+    MappedIntegrationRule<D,D> mir(*ir, *trafo, lh);
+    FlatVector<> elvec(nd, lh); elvec = 0.0;
+    FlatVector<> shape(nd, lh);
+    for (int i = 0; i < np; i++)
+      {
+        double x[3] = {0,0,0};
+        for (int d = 0; d < D; d++) x[d] = mir[i].GetPoint()(d);
+        double f = 0;
+        for (int m = 0; m < nmono; m++)
+          f += mono[4*m] * pow(x[0], mono[4*m+1]) * pow(x[1], mono[4*m+2]) * pow(x[2], mono[4*m+3]);
+        double pv = mir[i].GetMeasure() * (*ir)[i].Weight() * f;
+        fel.CalcShape((*ir)[i], shape);
+        elvec += pv * shape;
+      }
+    for (int i = 0; i < nd; i++) elvec_out[i] = elvec(i);
+    return np;
+  }
+};
+
+} // namespace
+
+extern "C" {
+
+int ref_select_rule(int et, int order, double * pts3, double * wts, int cap)
+{
+  try { return CopyRule(&SelectIntegrationRule(ELEMENT_TYPE(et), order), pts3, wts, cap); }
+  catch (...) { return -2; }
+}
+
+// cutint/straightcutrule.cpp:663-726
+int ref_cut_rule_untrafo(int et, const double * lset, int dt, int order, double * pts3, double * wts, int cap)
+{
+  LocalHeap & lh = GetLH(); HeapReset hr(lh);
+  try {
+    int nv = NV(ELEMENT_TYPE(et));
+    Vector<> lv(nv); for (int i = 0; i < nv; i++) lv(i) = lset[i];
+    auto ir = StraightCutIntegrationRuleUntransformed(lv, ELEMENT_TYPE(et), DOMAIN_TYPE(dt), order, FIND_OPTIMAL, lh);
+    return CopyRule(ir, pts3, wts, cap);
+  } catch (...) { return -2; }
+}
+
+// cutint/straightcutrule.cpp:580-661 (IF weights carry |F^-T n|)
+int ref_cut_rule(int et, const double * pmat, const double * lset, int dt, int order, double * pts3, double * wts, int cap)
+{
+  LocalHeap & lh = GetLH(); HeapReset hr(lh);
+  try {
+    const IntegrationRule * ir = nullptr;
+    if (et == ET_SEGM) { FE_ElementTransformation<1,1> * t; ir = TrafoRule<1>(ET_SEGM, pmat, lset, dt, order, lh, t); }
+    else if (et == ET_TRIG) { FE_ElementTransformation<2,2> * t; ir = TrafoRule<2>(ET_TRIG, pmat, lset, dt, order, lh, t); }
+    else if (et == ET_TET) { FE_ElementTransformation<3,3> * t; ir = TrafoRule<3>(ET_TET, pmat, lset, dt, order, lh, t); }
+    else return -4;
+    return CopyRule(ir, pts3, wts, cap);
+  } catch (...) { return -2; }
+}
+
+// xfem/cutinfo.cpp:79-111 : two order-0 rules -> part volumes -> domain + cut ratio.  returns DOMAIN_TYPE or -2
+int ref_cutinfo_element(int et, const double * pmat, const double * lset, double * ratio)
+{
+  double part_vol[2] = {0.0, 0.0};
+  double pts[3*64], wts[64];
+  for (int np : {1, 0})
+    {
+      int n = ref_cut_rule(et, pmat, lset, np, 0, pts, wts, 64);
+      if (n == -2) return -2;
+      for (int i = 0; i < n; i++) part_vol[np] += wts[i];
+    }
+  *ratio = part_vol[0] / (part_vol[0] + part_vol[1]);
+  if (part_vol[0] > 0.0) return part_vol[1] > 0.0 ? 2 : 0;
+  return 1;
+}
+
+int ref_h1_ndof(int et, int order)
+{
+  if (et == ET_TRIG) return H1HighOrderFE<ET_TRIG>(order).GetNDof();
+  if (et == ET_TET) return H1HighOrderFE<ET_TET>(order).GetNDof();
+  if (et == ET_SEGM) return H1HighOrderFE<ET_SEGM>(order).GetNDof();
+  return -1;
+}
+
+// shape (ndof) and reference-gradient dshape (ndof x dim) at a reference point
+int ref_h1_shape(int et, int order, const int * vnums, const double * ip3, double * shape, double * dshape)
+{
+  LocalHeap & lh = GetLH(); HeapReset hr(lh);
+  IntegrationPoint ip(ip3[0], ip3[1], ip3[2], 1.0);
+  if (et == ET_TRIG)
+    {
+      H1HighOrderFE<ET_TRIG> fel(order);
+      if (vnums) for (int i = 0; i < 3; i++) fel.SetVertexNumber(i, vnums[i]);
+      int nd = fel.GetNDof();
+      FlatVector<> s(nd, lh); FlatMatrixFixWidth<2> ds(nd, lh);
+      fel.CalcShape(ip, s); fel.CalcDShape(ip, ds);
+      for (int i = 0; i < nd; i++) { shape[i] = s(i); for (int d = 0; d < 2; d++) dshape[2*i+d] = ds(i,d); }
+      return nd;
+    }
+  if (et == ET_TET)
+    {
+      H1HighOrderFE<ET_TET> fel(order);
+      if (vnums) for (int i = 0; i < 4; i++) fel.SetVertexNumber(i, vnums[i]);
+      int nd = fel.GetNDof();
+      FlatVector<> s(nd, lh); FlatMatrixFixWidth<3> ds(nd, lh);
+      fel.CalcShape(ip, s); fel.CalcDShape(ip, ds);
+      for (int i = 0; i < nd; i++) { shape[i] = s(i); for (int d = 0; d < 3; d++) dshape[3*i+d] = ds(i,d); }
+      return nd;
+    }
+  return -1;
+}
+
+int ref_elmat_h1(int et, int fe_order, const int * vnums, const double * pmat, const double * lset, int dt, int intorder,
+                 double c_mass, double c_stiff, double * elmat)
+{
+  LocalHeap & lh = GetLH();
+  try {
+    if (et == ET_TRIG) return ElmatWork<ET_TRIG>::Elmat(fe_order, vnums, pmat, lset, dt, intorder, c_mass, c_stiff, elmat, lh);
+    if (et == ET_TET) return ElmatWork<ET_TET>::Elmat(fe_order, vnums, pmat, lset, dt, intorder, c_mass, c_stiff, elmat, lh);
+    return -4;
+  } catch (...) { return -2; }
+}
+
+int ref_elvec_h1(int et, int fe_order, const int * vnums, const double * pmat, const double * lset, int dt, int intorder,
+                 int nmono, const double * mono, double * elvec)
+{
+  LocalHeap & lh = GetLH();
+  try {
+    if (et == ET_TRIG) return ElmatWork<ET_TRIG>::Elvec(fe_order, vnums, pmat, lset, dt, intorder, nmono, mono, elvec, lh);
+    if (et == ET_TET) return ElmatWork<ET_TET>::Elvec(fe_order, vnums, pmat, lset, dt, intorder, nmono, mono, elvec, lh);
+    return -4;
+  } catch (...) { return -2; }
+}
+
+// ---------------------------------------------------------------------------------------------------------------
+// batched mesh-level drivers (CPU baseline; OpenMP threads stand in for netgen's TaskManager workers, each with its
+// own LocalHeap exactly like IterateRange's lh.Split, utils/ngsxstd.cpp:3-31)
+// ---------------------------------------------------------------------------------------------------------------
+
+static void GatherElement(int dim, const int * el2v, const double * vert, const double * lset_v, long e, double * pmat, double * lset)
+{
+  for (int i = 0; i < dim+1; i++)
+    {
+      int v = el2v[e*(dim+1)+i];
+      for (int d = 0; d < dim; d++) pmat[i*dim+d] = vert[(long)v*dim+d];
+      lset[i] = lset_v[v];
+    }
+}
+
+// CutInformation::Update element loop.  dom[e] in {0,1,2}; returns #elements on which the reference threw
+long ref_cutinfo_mesh(int dim, long ne, const int * el2v, const double * vert, const double * lset_v,
+                      signed char * dom, double * ratio, int nthreads)
+{
+  int et = dim == 2 ? ET_TRIG : ET_TET;
+  long nerr = 0;
+  if (nthreads > 0) omp_set_num_threads(nthreads);
+#pragma omp parallel for schedule(static) reduction(+:nerr)
+  for (long e = 0; e < ne; e++)
+    {
+      double pmat[12], lset[4];
+      GatherElement(dim, el2v, vert, lset_v, e, pmat, lset);
+      int r = ref_cutinfo_element(et, pmat, lset, &ratio[e]);
+      if (r < 0) { nerr++; dom[e] = -1; } else dom[e] = r;
+    }
+  return nerr;
+}
+
+// IntegrateX (cutint/python_cutint.cpp:41-68) with cf = sum_m coef_m x^a y^b z^c; deterministic per-element partials summed serially
+double ref_integrate_mesh(int dim, long ne, const int * el2v, const double * vert, const double * lset_v, int dt, int order,
+                          int nmono, const double * mono, int nthreads, long * npts_total)
+{
+  int et = dim == 2 ? ET_TRIG : ET_TET;
+  if (nthreads > 0) omp_set_num_threads(nthreads);
+  double sum = 0; long np = 0;
+#pragma omp parallel for schedule(static) reduction(+:sum,np)
+  for (long e = 0; e < ne; e++)
+    {
+      LocalHeap & lh = GetLH(); HeapReset hr(lh);
+      double pmat[12], lset[4];
+      GatherElement(dim, el2v, vert, lset_v, e, pmat, lset);
+      double lsum = 0; int n = 0;
+      auto work = [&](auto DD)
+        {
+          constexpr int D = decltype(DD)::value;
+          FE_ElementTransformation<D,D> * trafo;
+          const IntegrationRule * ir = TrafoRule<D>(ELEMENT_TYPE(et), pmat, lset, dt, order, lh, trafo);
+          if (!ir) return;
+          n = ir->Size();
+          MappedIntegrationRule<D,D> mir(*ir, *trafo, lh);
+          for (int i = 0; i < n; i++)
+            {
+              double x[3] = {0,0,0};
+              for (int d = 0; d < D; d++) x[d] = mir[i].GetPoint()(d);
+              double f = 0;
+              for (int m = 0; m < nmono; m++)
+                f += mono[4*m] * pow(x[0], mono[4*m+1]) * pow(x[1], mono[4*m+2]) * pow(x[2], mono[4*m+3]);
+              lsum += mir[i].GetMeasure() * (*ir)[i].Weight() * f;
+            }
+        };
+      if (dim == 2) work(std::integral_constant<int,2>()); else work(std::integral_constant<int,3>());
+      sum += lsum; np += n;
+    }
+  if (npts_total) *npts_total = np;
+  return sum;
+}
+
+// element matrices for a list of elements (els == nullptr: all), written densely elmats[k*nd*nd]; npts[k] = rule size or -1
+long ref_elmat_mesh(int dim, long nel, const long * els, const int * el2v, const double * vert, const double * lset_v,
+                    int fe_order, int dt, int intorder, double c_mass, double c_stiff, double * elmats, int * npts, int nthreads)
+{
+  int et = dim == 2 ? ET_TRIG : ET_TET;
+  int nd = ref_h1_ndof(et, fe_order);
+  if (nthreads > 0) omp_set_num_threads(nthreads);
+  long nnz = 0;
+#pragma omp parallel for schedule(dynamic,256) reduction(+:nnz)
+  for (long k = 0; k < nel; k++)
+    {
+      long e = els ? els[k] : k;
+      double pmat[12], lset[4];
+      GatherElement(dim, el2v, vert, lset_v, e, pmat, lset);
+      int vn[4]; for (int i = 0; i < dim+1; i++) vn[i] = el2v[e*(dim+1)+i];
+      int r = ref_elmat_h1(et, fe_order, vn, pmat, lset, dt, intorder, c_mass, c_stiff, elmats + (size_t)k*nd*nd);
+      if (npts) npts[k] = r;
+      if (r < 0) for (int i = 0; i < nd*nd; i++) elmats[(size_t)k*nd*nd+i] = 0.0;
+      else nnz++;
+    }
+  return nnz;
+}
+
+// Full assemble-to-CSR on the host: reference element matrix per element, then the row-search "+=" of
+// SparseMatrixTM::AddElementMatrix (NGS/linalg/sparsematrix_impl.hpp:63-103: columns sorted, linear scan of the CSR row),
+// colour by colour (NGS/comp/fespace.cpp:1540-1566: one parallel loop per colour).
+long ref_assemble_csr(int dim, const int * el2v, const double * vert, const double * lset_v,
+                      int fe_order, const int * el2dof, int dt, int intorder, double c_mass, double c_stiff,
+                      int ncolors, const long * color_ptr, const int * color_els,
+                      const long * rowptr, const int * colidx, double * vals, int nthreads)
+{
+  int et = dim == 2 ? ET_TRIG : ET_TET;
+  int nd = ref_h1_ndof(et, fe_order);
+  if (nthreads > 0) omp_set_num_threads(nthreads);
+  long nass = 0;
+  for (int c = 0; c < ncolors; c++)
+    {
+#pragma omp parallel for schedule(dynamic,64) reduction(+:nass)
+      for (long k = color_ptr[c]; k < color_ptr[c+1]; k++)
+        {
+          long e = color_els[k];
+          double pmat[12], lset[4], elmat[400];
+          GatherElement(dim, el2v, vert, lset_v, e, pmat, lset);
+          int vn[4]; for (int i = 0; i < dim+1; i++) vn[i] = el2v[e*(dim+1)+i];
+          int r = ref_elmat_h1(et, fe_order, vn, pmat, lset, dt, intorder, c_mass, c_stiff, elmat);
+          if (r < 0) continue;
+          nass++;
+          const int * dn = el2dof + e*nd;
+          int map[20]; for (int i = 0; i < nd; i++) map[i] = i;
+          std::sort(map, map+nd, [&](int a, int b) { return dn[a] < dn[b]; });
+          for (int i = 0; i < nd; i++)
+            {
+              long k0 = rowptr[dn[i]];
+              for (int j1 = 0; j1 < nd; j1++)
+                {
+                  int j = map[j1];
+                  while (colidx[k0] != dn[j]) k0++;
+                  vals[k0] += elmat[i*nd+j];
+                }
+            }
+        }
+    }
+  return nass;
+}
+
+int ref_max_threads() { return omp_get_max_threads(); }
+
+} // extern "C"
