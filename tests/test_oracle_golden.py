@@ -1,0 +1,95 @@
+"""CPU oracle (oracle/ngsx_oracle.c) against the committed golden vectors produced by the compiled reference
+(tools/gen_golden.py -> tests/golden/*.npz).  Bit-exact on flags and point counts; 1e-12 relative on values."""
+import numpy as np
+import pytest
+
+from oracle import orc
+from ngsxfem_b200 import meshes
+
+RTOL = 1e-12
+
+
+def relerr(a, b):
+    s = np.abs(b).max() if b.size else 0.0
+    return 0.0 if s == 0 else np.abs(a - b).max() / s
+
+
+@pytest.mark.parametrize("dim", [2, 3])
+def test_cutinfo_single(golden_single, dim):
+    g = golden_single
+    pm, ls = g[f"d{dim}_pmat"], g[f"d{dim}_lset"]
+    for t in range(len(pm)):
+        d, r = orc.cutinfo_element(dim, pm[t], ls[t])
+        assert d == g[f"d{dim}_dom"][t]
+        if d >= 0:
+            assert abs(r - g[f"d{dim}_ratio"][t]) <= 1e-12
+
+
+@pytest.mark.parametrize("dim", [2, 3])
+@pytest.mark.parametrize("dt", [0, 1, 2])
+def test_cut_rules_single(golden_single, dim, dt):
+    g = golden_single
+    pm, ls = g[f"d{dim}_pmat"], g[f"d{dim}_lset"]
+    for order in (0, 1, 2, 3, 4, 5, 6):
+        npts = g[f"d{dim}_dt{dt}_o{order}_npts"]
+        P, W = g[f"d{dim}_dt{dt}_o{order}_pts"], g[f"d{dim}_dt{dt}_o{order}_wts"]
+        off = 0
+        for t in range(len(pm)):
+            n, p, w = orc.cut_rule(dim, pm[t], ls[t], dt, order)
+            assert n == npts[t], (t, ls[t], n, npts[t])           # bit-exact count incl. -1 (no rule) / -2 (reference throws)
+            if n > 0:
+                assert np.abs(p - P[off:off + n]).max() <= 1e-14
+                assert relerr(w, W[off:off + n]) <= RTOL
+                off += n
+
+
+@pytest.mark.parametrize("dim", [2, 3])
+@pytest.mark.parametrize("fo", [1, 2, 3])
+def test_elmat_elvec_single(golden_single, dim, fo):
+    g = golden_single
+    pm, ls, vn = g[f"d{dim}_pmat"], g[f"d{dim}_lset"], g[f"d{dim}_vnums"]
+    mono = [(1.0, 0, 0, 0), (2.0, 1, 2, 0), (-0.5, 0, 0, 1)]
+    for dt in (0, 1, 2):
+        em, ev, npt = g[f"d{dim}_p{fo}_dt{dt}_elmat"], g[f"d{dim}_p{fo}_dt{dt}_elvec"], g[f"d{dim}_p{fo}_dt{dt}_npts"]
+        for t in range(len(pm)):
+            n, m = orc.elmat_h1(dim, fo, vn[t], pm[t], ls[t], dt, 2 * fo, 1.25, 0.75)
+            assert n == npt[t]
+            if n > 0:
+                assert relerr(m, em[t]) <= RTOL
+                k, v = orc.elvec_h1(dim, fo, vn[t], pm[t], ls[t], dt, 2 * fo, mono)
+                assert np.abs(v - ev[t]).max() <= RTOL * max(np.abs(ev[t]).max(), np.abs(m).max())
+
+
+def _mesh(tag, g):
+    if tag == "m3":
+        m = meshes.MakeStructured3DMesh(6)
+    else:
+        m = meshes.MakeStructured2DMesh(12, lo=(-1, -1), hi=(1, 1))
+    return m, g[f"{tag}_lset"]
+
+
+@pytest.mark.parametrize("tag", ["m2", "m3"])
+def test_small_mesh(golden_meshes, tag):
+    g = golden_meshes
+    m, ls = _mesh(tag, g)
+    el2v, vert = m.el2v.numpy(), m.vert.numpy()
+    dom, ratio, nerr = orc.cutinfo_mesh(m.dim, el2v, vert, ls)
+    assert nerr == 0
+    assert np.array_equal(dom, g[f"{tag}_dom"])
+    assert np.abs(ratio - g[f"{tag}_ratio"]).max() <= 1e-12
+    for dt in (0, 1, 2):
+        for order in (0, 2, 4):
+            ref = g[f"{tag}_int_dt{dt}_o{order}"]
+            v, npt = orc.integrate_mesh(m.dim, el2v, vert, ls, dt, order, [(1.0, 0, 0, 0)])
+            assert npt == int(ref[2])
+            assert abs(v - ref[0]) <= RTOL * abs(ref[0])
+            v2, _ = orc.integrate_mesh(m.dim, el2v, vert, ls, dt, order,
+                                       [(1.0, 2, 0, 0), (0.5, 0, 1, 1 if m.dim == 3 else 0)])
+            assert abs(v2 - ref[1]) <= RTOL * abs(ref[1])
+        for fo in (1, 2):
+            em, npts = orc.elmat_mesh(m.dim, el2v, vert, ls, fo, dt, 2 * fo, 1.0, 1.0)
+            assert np.array_equal(npts, g[f"{tag}_p{fo}_dt{dt}_npts"])
+            gm = g[f"{tag}_p{fo}_dt{dt}_elmat"]
+            scale = np.abs(gm).reshape(len(gm), -1).max(axis=1)
+            err = np.abs(em - gm).reshape(len(gm), -1).max(axis=1)
+            assert (err <= RTOL * np.maximum(scale, 1e-300)).all()

@@ -1,0 +1,160 @@
+"""CPU oracle against the reference's OWN known-answer tests for the path:
+tests/pytests/test_localgeom.py:24-45, test_straightcutrule.py:11-31, 111-126, 134-154, 166-185, 191-207, 218-235,
+242-280, test_xfes_ndof.py:5-21 -- same level sets, same analytic values, same tolerances."""
+from math import pi, sqrt
+
+import numpy as np
+import pytest
+
+from oracle import orc
+from ngsxfem_b200 import meshes
+
+NEG, POS, IF = 0, 1, 2
+
+
+def p1(levelset, vert, eps=1e-14):
+    v = levelset(*vert.T)
+    return np.where(np.abs(v) < eps, eps, v)
+
+
+def integrate(m, ls, dt, order, mono=None):
+    return orc.integrate_mesh(m.dim, m.el2v.numpy(), m.vert.numpy(), ls, dt, order, mono)[0]
+
+
+def test_cut_triangle_localgeom():
+    # test_localgeom.py:24-45: triangle (0,0),(1,0),(0,1) in 4 elements, levelset x+y-0.25, orders 0..15
+    vert = np.array([[0, 0], [1, 0], [0, 1], [.5, 0], [.5, .5], [0, .5]], dtype=float)
+    el2v = np.array([[0, 3, 5], [3, 1, 4], [5, 4, 2], [3, 4, 5]], dtype=np.int32)
+    ls = p1(lambda x, y: x + y - 0.25, vert)
+    for order in range(16):
+        neg = orc.integrate_mesh(2, el2v, vert, ls, NEG, order)[0]
+        pos = orc.integrate_mesh(2, el2v, vert, ls, POS, order)[0]
+        tol = 5e-16 * (order + 1) ** 2
+        assert abs(neg - 1 / 32) < tol
+        assert abs(pos - 0.5 + 1 / 32) < tol
+        assert abs(neg + pos - 0.5) < tol
+
+
+@pytest.mark.parametrize("domain", [NEG, POS, IF])
+@pytest.mark.parametrize("alpha", [2, 4, 8])
+def test_polynomial_segm(domain, alpha):
+    # test_straightcutrule.py:11-31 (1D): the oracle's 1D rule on the unit segment, integrand x^alpha
+    x_ast = 0.78522
+    ref = {POS: x_ast ** (alpha + 1) / (alpha + 1), NEG: (1 - x_ast ** (alpha + 1)) / (alpha + 1), IF: x_ast ** alpha}
+    pm = np.array([[0.0], [1.0]])                       # Make1DMesh(1): vertices 0 and 1
+    ls = np.array([x_ast - 0.0, x_ast - 1.0])
+    n, pts, w = orc.cut_rule(1, pm, ls, domain, alpha)
+    xs = pm[1, 0] + (pm[0, 0] - pm[1, 0]) * pts[:, 0]
+    val = float(np.sum(w * xs ** alpha)) * abs(pm[0, 0] - pm[1, 0])
+    assert abs(val - ref[domain]) < 5e-15 * (alpha + 1) ** 2
+
+
+@pytest.mark.parametrize("order", [2, 4, 8])
+@pytest.mark.parametrize("domain", [NEG, POS, IF])
+@pytest.mark.parametrize("N", [1, 10, 30])
+def test_straight_cut_2d(order, domain, N):
+    # test_straightcutrule.py:111-126 (trig branch)
+    m = meshes.MakeStructured2DMesh(N)
+    ls = p1(lambda x, y: 1 - 2 * x - 2 * y, m.vert.numpy())
+    ref = {NEG: 7 / 8, POS: 1 / 8, IF: 1 / sqrt(2)}
+    assert abs(integrate(m, ls, domain, order) - ref[domain]) < 5e-15 * (order + 1) ** 2
+
+
+@pytest.mark.parametrize("domain", [IF, NEG, POS])
+@pytest.mark.parametrize("dim", [0, 1])
+@pytest.mark.parametrize("eps", [1e-1, 1e-2, 5e-3, 1e-3, 0])
+def test_orth_cut_2d_epsiloned(domain, dim, eps):
+    # test_straightcutrule.py:134-154
+    m = meshes.MakeStructured2DMesh(1)
+    f = (lambda x, y: 1 - 2 * x + eps * (y - 0.5)) if dim == 0 else (lambda x, y: 1 - 2 * y + eps * (x - 0.5))
+    ls = p1(f, m.vert.numpy())
+    ref = {NEG: 0.5, POS: 0.5, IF: sqrt(1 + eps * eps / 4)}
+    assert abs(integrate(m, ls, domain, 2) - ref[domain]) < 5e-15 * 9
+
+
+@pytest.mark.parametrize("order", [2, 4, 8])
+@pytest.mark.parametrize("domain", [NEG, POS])
+@pytest.mark.parametrize("alpha", [0, 1, 2])
+@pytest.mark.parametrize("dim", [0, 1])
+def test_straight_cut_2d_polynomial(order, domain, alpha, dim):
+    # test_straightcutrule.py:166-185
+    m = meshes.MakeStructured2DMesh(1)
+    ls = p1(lambda x, y: 1 - 2 * x - 2 * y, m.vert.numpy())
+    val_pos = 2 ** (-alpha - 2) / (alpha * alpha + 3 * alpha + 2)
+    ref = {POS: val_pos, NEG: 1 / (alpha + 1) - val_pos}
+    mono = [(1.0, alpha if dim == 0 else 0, alpha if dim == 1 else 0, 0)]
+    assert abs(integrate(m, ls, domain, order, mono) - ref[domain]) < 5e-15 * (order + 1) ** 2
+
+
+@pytest.mark.parametrize("order", [2, 4, 8])
+@pytest.mark.parametrize("domain", [NEG, POS, IF])
+def test_straight_cut_3d(order, domain):
+    # test_straightcutrule.py:191-207 (tet branch)
+    m = meshes.MakeStructured3DMesh(1)
+    ls = p1(lambda x, y, z: 1 - 2 * x - 2 * y - 2 * z, m.vert.numpy())
+    ref = {POS: 1 / 48, NEG: 47 / 48, IF: sqrt(3) / 8}
+    assert abs(integrate(m, ls, domain, order) - ref[domain]) < 5e-15 * (order + 1) ** 2
+
+
+@pytest.mark.parametrize("domain", [NEG, POS])
+@pytest.mark.parametrize("alpha", [0, 1, 2])
+@pytest.mark.parametrize("dim", [0, 1, 2])
+def test_straight_cut_3d_polynomial(domain, alpha, dim):
+    # test_straightcutrule.py:218-235
+    order = 4
+    m = meshes.MakeStructured3DMesh(1)
+    ls = p1(lambda x, y, z: 1 - 2 * x - 2 * y - 2 * z, m.vert.numpy())
+    val_pos = 2 ** (-alpha - 3) / (alpha ** 3 + 6 * alpha * alpha + 11 * alpha + 6)
+    ref = {POS: val_pos, NEG: 1 / (alpha + 1) - val_pos}
+    e = [0, 0, 0]
+    e[dim] = alpha
+    assert abs(integrate(m, ls, domain, order, [(1.0, *e)]) - ref[domain]) < 5e-15 * (order + 1) ** 2
+
+
+@pytest.mark.parametrize("domain", [NEG, POS, IF])
+@pytest.mark.parametrize("dim", [0, 1])
+def test_orth_cut_2d(domain, dim):
+    # test_straightcutrule.py:242-257
+    m = meshes.MakeStructured2DMesh(1)
+    ls = p1((lambda x, y: 1 - 3 * x) if dim == 0 else (lambda x, y: 1 - 3 * y), m.vert.numpy())
+    ref = {NEG: 2 / 3, POS: 1 / 3, IF: 1.0}
+    assert abs(integrate(m, ls, domain, 2) - ref[domain]) < 5e-15 * 9
+
+
+@pytest.mark.parametrize("domain", [NEG, POS])
+@pytest.mark.parametrize("dim", [0, 1, 2])
+def test_orth_cut_3d(domain, dim):
+    # test_straightcutrule.py:265-280
+    m = meshes.MakeStructured3DMesh(1)
+    fs = [lambda x, y, z: 1 - 2 * x, lambda x, y, z: 1 - 2 * y, lambda x, y, z: 1 - 2 * z]
+    ls = p1(fs[dim], m.vert.numpy())
+    assert abs(integrate(m, ls, domain, 2) - 0.5) < 5e-15 * 9
+
+
+@pytest.mark.parametrize("order", [2, 4, 8])
+@pytest.mark.parametrize("domain", [NEG, POS, IF])
+def test_circle_eoc(order, domain):
+    # test_straightcutrule.py:37-68 (trig branch): second-order convergence of the P1 geometry
+    r = 0.6
+    ref = {POS: 1 - pi * r * r / 4, NEG: pi * r * r / 4, IF: r * pi / 2}
+    errs = []
+    for i in range(8):
+        m = meshes.MakeStructured2DMesh(2 ** i)
+        ls = p1(lambda x, y: np.sqrt(x * x + y * y) - r, m.vert.numpy())
+        errs.append(abs(integrate(m, ls, domain, order) - ref[domain]))
+    eoc = [np.log(errs[i + 1] / errs[i]) / np.log(0.5) for i in range(7)]
+    assert np.mean(eoc[1:]) > 1.75
+
+
+def test_xfes_ndof():
+    # test_xfes_ndof.py:5-21: XFESpace.ndof = #P1 dofs of IF elements = 7 (2D 4x4) / 35 (3D 4^3, cylinder level set)
+    m = meshes.MakeStructured2DMesh(4, lo=(-1, -1), hi=(1, 1))
+    ls = p1(lambda x, y: np.sqrt(x * x + y * y) - 1 / 3, m.vert.numpy())
+    dom, _, nerr = orc.cutinfo_mesh(2, m.el2v.numpy(), m.vert.numpy(), ls)
+    assert nerr == 0 and m.nv == 25
+    assert orc.dofs_of_elements(m.el2v.numpy(), m.nv, dom == IF).sum() == 7
+    m = meshes.MakeStructured3DMesh(4, lo=(-1, -1, -1), hi=(1, 1, 1))
+    ls = p1(lambda x, y, z: np.sqrt(x * x + y * y) - 1 / 3, m.vert.numpy())
+    dom, _, nerr = orc.cutinfo_mesh(3, m.el2v.numpy(), m.vert.numpy(), ls)
+    assert nerr == 0 and m.nv == 125
+    assert orc.dofs_of_elements(m.el2v.numpy(), m.nv, dom == IF).sum() == 35

@@ -1,0 +1,51 @@
+"""Randomised cross-check of the C restatement (oracle/ngsx_oracle.c) against the reference's own sources compiled
+in place (oracle/_ref/libngsxref.so).  Skipped where the compiled reference is absent."""
+import numpy as np
+import pytest
+
+from oracle import orc, refload
+
+pytestmark = pytest.mark.skipif(not refload.available(), reason="oracle/_ref not built (needs /root/reference)")
+
+
+def nice_simplex(rng, dim):
+    pm = np.vstack([np.eye(dim), np.zeros(dim)]) + 0.15 * rng.uniform(-1, 1, (dim + 1, dim))
+    return pm * rng.uniform(0.05, 0.5) + rng.uniform(-1, 1, dim)
+
+
+@pytest.mark.parametrize("dim", [1, 2, 3])
+def test_rules_random(dim):
+    rng = np.random.default_rng(7 + dim)
+    for t in range(400):
+        ls = rng.uniform(-1, 1, dim + 1)
+        if t % 7 == 0:
+            ls[rng.integers(dim + 1)] = 1e-14
+        pm = nice_simplex(rng, dim)
+        for dt in (0, 1, 2):
+            for order in (0, 2, 3, 5, 8):
+                a = orc.cut_rule(dim, pm, ls, dt, order)
+                b = orc.cut_rule(dim, pm, ls, dt, order, impl="ref")
+                assert a[0] == b[0]
+                if a[0] > 0:
+                    assert np.abs(a[1] - b[1]).max() <= 1e-14
+                    assert np.abs(a[2] - b[2]).max() <= 1e-12 * np.abs(b[2]).max()
+
+
+@pytest.mark.parametrize("dim", [2, 3])
+@pytest.mark.parametrize("fo", [1, 2, 3])
+def test_shapes_and_elmat_random(dim, fo):
+    rng = np.random.default_rng(11 * dim + fo)
+    for t in range(100):
+        vn = rng.permutation(50)[:dim + 1]
+        xi = rng.uniform(0, 1, dim)
+        xi /= xi.sum() + rng.uniform(0, 1)
+        a, b = orc.h1_shape(dim, fo, vn, xi), orc.h1_shape(dim, fo, vn, xi, impl="ref")
+        assert np.abs(a[0] - b[0]).max() <= 1e-14 and np.abs(a[1] - b[1]).max() <= 1e-14
+        pm = nice_simplex(rng, dim)
+        ls = rng.uniform(-1, 1, dim + 1)
+        for dt in (0, 1, 2):
+            a = orc.elmat_h1(dim, fo, vn, pm, ls, dt, 2 * fo, 1.3, 0.7)
+            b = orc.elmat_h1(dim, fo, vn, pm, ls, dt, 2 * fo, 1.3, 0.7, impl="ref")
+            assert a[0] == b[0]
+            if a[0] > 0:
+                assert np.abs(a[1] - b[1]).max() <= 1e-12 * np.abs(b[1]).max()
