@@ -1,0 +1,187 @@
+/* ngsx_abi.h -- C ABI of libngsx_b200.so: the B200-native (sm_100a) cut-FEM assembly hot path of ngsxfem.
+ *
+ * Batched replacement for the per-element virtual calls of the reference: one call per
+ * CutInfo.Update / Assemble / Integrate over flat device arrays.  Plain pointers and sizes only; no C++/torch
+ * types cross this boundary.  All pointers are DEVICE pointers unless the name starts with h_.  Every entry point
+ * returns 0 on success or a negative ngsx_status; ngsx_last_error() returns a thread-local message.  `stream` is a
+ * cudaStream_t passed as void* (NULL = legacy default stream); calls are asynchronous on it unless noted.
+ *
+ * Reference interfaces replaced (paths relative to the ngsxfem tree; NGS/ = external_dependencies/ngsolve/):
+ *   enums                     utils/ngsxstd.hpp:8-78, python/python_ngsxfem.cpp:14-37
+ *   ngsx_interpolate_p1_*     utils/p1interpol.cpp:25-96            (InterpolateToP1, utils/python_utils.cpp:21-81)
+ *   ngsx_classify             xfem/cutinfo.cpp:54-120               (CutInfo.Update, xfem/python_xfem.cpp:57-70)
+ *   ngsx_node_marks           xfem/cutinfo.cpp:122-186
+ *   ngsx_rule_count/_fill     cutint/xintegration.cpp:13-80, cutint/straightcutrule.cpp:580-726
+ *   ngsx_elmat_h1             xfem/symboliccutbfi.cpp:73-315        (CalcElementMatrixAdd, xfem/symboliccutbfi.hpp:42-58)
+ *   ngsx_elvec_h1             xfem/symboliccutlfi.cpp:52-158        (CalcElementVector, xfem/symboliccutlfi.hpp:38-55)
+ *   ngsx_csr_graph_*          utils/restrictedblf.cpp:22-138        (RestrictedBilinearForm::GetGraph)
+ *   ngsx_color_groups         NGS/comp/fespace.cpp:598-705          (FESpace element colouring)
+ *   ngsx_assemble_csr_h1      NGS/comp/bilinearform.cpp:1117-1575 + NGS/linalg/sparsematrix_impl.hpp:63-103
+ *   ngsx_assemble_vec_h1      NGS/comp/linearform.cpp:209-243
+ *   ngsx_integrate            cutint/python_cutint.cpp:20-72        (IntegrateX)
+ *   ngsx_facets_neighbor_types, ngsx_elements_with_neighbor_facets, ngsx_dofs_of_elements
+ *                             xfem/cutinfo.cpp:191-304              (xfem/python_xfem.cpp:168-318)
+ *   ngsx_facetpatch_elmat_h1  xfem/symboliccutbfi.cpp:1115-1411     (CalcFacetMatrix, xfem/symboliccutbfi.hpp:253-259)
+ *
+ * Bit arrays are uint32 words, bit i of the array = word i/32, bit i%32: layout-compatible with netgen's
+ * ngcore::BitArray (NG/libsrc/core/bitarray.hpp:150-155: byte i/8, mask 1<<(i%8)) on little-endian hosts.
+ */
+#ifndef NGSX_ABI_H
+#define NGSX_ABI_H
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define NGSX_ABI_VERSION 1
+
+/* utils/ngsxstd.hpp:14-17 */
+enum ngsx_domain_type { NGSX_NEG = 0, NGSX_POS = 1, NGSX_IF = 2 };
+/* utils/ngsxstd.hpp:24-33 (bit mask: NEG=1, POS=2, IF=4) */
+enum ngsx_combined_domain_type {
+  NGSX_CDOM_NO = 0, NGSX_CDOM_NEG = 1, NGSX_CDOM_POS = 2, NGSX_CDOM_UNCUT = 3,
+  NGSX_CDOM_IF = 4, NGSX_CDOM_HASNEG = 5, NGSX_CDOM_HASPOS = 6, NGSX_CDOM_ANY = 7 };
+
+enum ngsx_status {
+  NGSX_OK = 0,
+  NGSX_ERR_ARG = -1,          /* bad argument (dimension, order, null pointer, ...) */
+  NGSX_ERR_UNSUPPORTED = -2,  /* form / element / order outside the CUDA path: no CPU fallback by charter */
+  NGSX_ERR_CUDA = -3,         /* CUDA runtime error (message has cudaGetErrorString) */
+  NGSX_ERR_DEGENERATE = -4,   /* level set the reference throws on (vertex value exactly 0 on a cut element, all-zero element) */
+  NGSX_ERR_CAPACITY = -5      /* caller buffer too small / too many colours */
+};
+
+typedef struct ngsx_mesh {
+  int32_t dim;              /* 2: triangles (ET_TRIG), 3: tetrahedra (ET_TET) */
+  int32_t _pad;
+  int64_t ne, nv;
+  const double  *vert;      /* [nv][dim] */
+  const int32_t *el2v;      /* [ne][dim+1], local vertex order of the reference mesh */
+} ngsx_mesh;
+
+/* bilinear form on scalar H1:  sum of
+ *   c_stiff * h^hpow_stiff * grad(u).grad(v) + c_mass * h^hpow_mass * u v
+ * + c_nitsche * h^hpow_nitsche * ( (grad(u).n) v + (grad(v).n) u ),   n = grad(lset_p1)/|grad(lset_p1)|,  h = |det J|^(1/dim)
+ * (the coefficient functions of py_tutorials/fictdom_ghostpen.py:86-96; elementwise constant => evaluated once per element
+ * like xfem/symboliccutbfi.cpp:205-214). */
+typedef struct ngsx_form_h1 {
+  double  c_mass, c_stiff, c_nitsche;
+  int32_t hpow_mass, hpow_stiff, hpow_nitsche, _pad;
+} ngsx_form_h1;
+
+/* polynomial coefficient function  f(x) = sum_{m<nterms} coef[m] * x^ex[m][0] * y^ex[m][1] * z^ex[m][2] */
+#define NGSX_POLY_MAXTERMS 8
+typedef struct ngsx_poly {
+  int32_t nterms, _pad;
+  double  coef[NGSX_POLY_MAXTERMS];
+  int32_t ex[NGSX_POLY_MAXTERMS][3];
+} ngsx_poly;
+
+/* analytic level sets for the CoefficientFunction branch of InterpolateToP1 */
+enum ngsx_lset_kind {
+  NGSX_LSET_AFFINE = 0,   /* p[0] + p[1] x + p[2] y + p[3] z */
+  NGSX_LSET_SPHERE = 1,   /* |x - (p[0],p[1],p[2])| - p[3]            (2D: circle, p[2] ignored) */
+  NGSX_LSET_RING   = 2,   /* | |x - c| - p[3] | - p[4]                (fictdom_ghostpen.py:28-33: rc, rr) */
+  NGSX_LSET_CYLZ   = 3    /* sqrt((x-p0)^2+(y-p1)^2) - p[3]           (tests/pytests/test_xfes_ndof.py:16) */
+};
+
+int         ngsx_abi_version(void);
+const char *ngsx_last_error(void);
+/* number of kernels launched by this library in the calling process since load (bench.py "gpu_launches") */
+int64_t     ngsx_launch_count(void);
+
+/* ---- (a-0) InterpolateToP1 ------------------------------------------------------------------------------------ */
+/* GridFunction branch: out[v] = in[v], |out| < eps -> eps   (utils/p1interpol.cpp:74-90) */
+int ngsx_interpolate_p1_clamp(int64_t nv, const double *in, double eps, double *out, void *stream);
+/* CoefficientFunction branch for an analytic level set evaluated at the vertices, then the same clamp */
+int ngsx_interpolate_p1_cf(const ngsx_mesh *mesh, int kind, const double *h_params /*[8]*/, double eps, double *out, void *stream);
+
+/* ---- (a) CutInfo.Update ---------------------------------------------------------------------------------------- */
+/* cdom_words: [8][nwords] with nwords = (ne+31)/32, indexed by ngsx_combined_domain_type (row NO stays 0, ANY all ones);
+ * dom: [ne] int8 ngsx_domain_type; ratio: [ne] cut ratio vol_NEG/(vol_NEG+vol_POS) of xfem/cutinfo.cpp:91;
+ * err: [2] int64 {number of degenerate elements, smallest such element number or -1}.  Any output may be NULL.
+ * Degenerate elements (the reference throws) are counted in err and get dom = -1, no bits. */
+int ngsx_classify(const ngsx_mesh *mesh, const double *lset_v, uint32_t *cdom_words, int8_t *dom, double *ratio,
+                  int64_t *err, void *stream);
+/* cut_neighboring_node / dom_of_node for one node type (xfem/cutinfo.cpp:122-186): el2node [ne][npe];
+ * cut_nb_words [(nnodes+31)/32] is OR-ed (must be zeroed by the caller), dom_of_node [nnodes] int32 must be pre-filled
+ * with IF(2); it is lowered with an integer atomicMin (NEG < POS < IF), which makes the reference's racy last-writer
+ * store (cutinfo.cpp:163-183) deterministic.  cell_mode != 0: node == element, dom_of_node = ratio > 0.5 ? NEG : POS (:176-181).
+ * err[1] of ngsx_classify / ngsx_rule_count is INT64_MAX when no element is degenerate. */
+int ngsx_node_marks(int64_t ne, int32_t npe, const int32_t *el2node, const int8_t *dom, const double *ratio,
+                    int64_t nnodes, int cell_mode, uint32_t *cut_nb_words, int32_t *dom_of_node, void *stream);
+
+/* ---- (b) straight-cut quadrature ------------------------------------------------------------------------------- */
+/* npts[e] = size of the reference's rule for (dt, order) on element e; 0 where the reference returns nullptr.
+ * err as in ngsx_classify (may be NULL). */
+int ngsx_rule_count(const ngsx_mesh *mesh, const double *lset_v, int dt, int order, int32_t *npts, int64_t *err, void *stream);
+/* out[i] = sum_{k<i} in[k] (n+1 outputs, out[n] = total) */
+int ngsx_exclusive_scan(int64_t n, const int32_t *in, int64_t *out, void *stream);
+/* points (reference coordinates, [total][3]) and weights ([total]) at offs[e], in the reference's emission order.
+ * transform_if != 0: IF weights carry |F^-T n| like StraightCutIntegrationRule (straightcutrule.cpp:558-576);
+ *               == 0: StraightCutIntegrationRuleUntransformed (:663-726).
+ * emit_uncut == 0: uncut elements (whose rule is NGSolve's static table) are skipped (their offs range must be empty). */
+int ngsx_rule_fill(const ngsx_mesh *mesh, const double *lset_v, int dt, int order, int transform_if, int emit_uncut,
+                   const int64_t *offs, double *pts3, double *wts, void *stream);
+
+/* ---- (c) element matrices / vectors ---------------------------------------------------------------------------- */
+/* els: [nlist] element numbers (NULL: 0..nlist-1).  elmats: [nlist][nd][nd] row-major (rows = test functions), zero where
+ * the reference adds nothing; npts (may be NULL): rule size used per listed element.  fe_order 1..2, H1HighOrderFE basis.
+ * intorder < 0: the reference's default 2*fe_order - (difforders) is NOT guessed here -- the caller passes it. */
+int ngsx_elmat_h1(const ngsx_mesh *mesh, const double *lset_v, int fe_order, int dt, int intorder, const ngsx_form_h1 *h_form,
+                  int64_t nlist, const int32_t *els, double *elmats, int32_t *npts, void *stream);
+int ngsx_elvec_h1(const ngsx_mesh *mesh, const double *lset_v, int fe_order, int dt, int intorder, const ngsx_poly *h_f,
+                  int64_t nlist, const int32_t *els, double *elvecs, int32_t *npts, void *stream);
+
+/* ---- (d) CSR graph, colouring, scatter ------------------------------------------------------------------------- */
+typedef struct ngsx_graph ngsx_graph;   /* opaque, host object owning temporary device buffers */
+int ngsx_csr_graph_create(int64_t ndof, ngsx_graph **out);
+/* add the couplings of a dof table [n][nd] (element dofs of marked elements, or the merged dofs of facet patches) */
+int ngsx_csr_graph_add_table(ngsx_graph *g, int64_t n, int32_t nd, const int32_t *table, void *stream);
+/* sort + unique; synchronises the stream; returns nnz */
+int ngsx_csr_graph_finalize(ngsx_graph *g, int64_t *h_nnz, void *stream);
+int ngsx_csr_graph_export(ngsx_graph *g, int64_t *rowptr /*[ndof+1]*/, int32_t *colidx /*[nnz]*/, void *stream);
+int ngsx_csr_graph_destroy(ngsx_graph *g);
+/* slots[k][i*nd+j] = position of (table[k][i], table[k][j]) in the CSR arrays (binary search of the sorted row) */
+int ngsx_slot_map(int64_t n, int32_t nd, const int32_t *table, const int64_t *rowptr, const int32_t *colidx,
+                  int32_t *slots, void *stream);
+/* HOST function (all pointers host): greedy colouring of groups of `group` consecutive list entries such that two groups
+ * of one colour share no dof (group == 1: NGSolve's element colouring).  h_table [n][nd] = dofs of list entry k.
+ * Writes the colour-sorted permutation h_perm[n] (positions into the input list, groups kept contiguous) and
+ * h_color_ptr[ncolors+1] (offsets into h_perm, in list entries).  cap_colors = capacity of h_color_ptr minus 1. */
+int ngsx_color_groups(int64_t n, int32_t nd, const int32_t *h_table, int64_t ndof, int32_t group,
+                      int64_t *h_perm, int64_t *h_color_ptr, int32_t cap_colors, int32_t *h_ncolors);
+/* fused cut rule -> element matrix -> "+=" into CSR values, colour by colour, no floating-point atomics.
+ * els/slots are in colour-sorted order (ngsx_color_groups), h_color_ptr is a HOST array. */
+int ngsx_assemble_csr_h1(const ngsx_mesh *mesh, const double *lset_v, int fe_order, int dt, int intorder,
+                         const ngsx_form_h1 *h_form, int64_t nlist, const int32_t *els, const int32_t *slots,
+                         int32_t ncolors, const int64_t *h_color_ptr, int32_t group, double *vals, void *stream);
+int ngsx_assemble_vec_h1(const ngsx_mesh *mesh, const double *lset_v, int fe_order, int dt, int intorder,
+                         const ngsx_poly *h_f, int64_t nlist, const int32_t *els, const int32_t *el2dof_list /*[nlist][nd]*/,
+                         int32_t ncolors, const int64_t *h_color_ptr, int32_t group, double *vec, void *stream);
+
+/* ---- Integrate ------------------------------------------------------------------------------------------------- */
+/* out[0] = sum_e sum_q |det J_e| w_q f(x_q) over the (dt, order) cut rule; fixed-shape tree reduction (bitwise
+ * reproducible run to run).  out is a device double. */
+int ngsx_integrate(const ngsx_mesh *mesh, const double *lset_v, int dt, int order, const ngsx_poly *h_f, double *out, void *stream);
+
+/* ---- facet / element / dof marking ----------------------------------------------------------------------------- */
+/* facet2el [nf][2], -1 = no neighbour (boundary facet: bnd_val_a/b are used, xfem/cutinfo.cpp:238-241) */
+int ngsx_facets_neighbor_types(int64_t nf, const int32_t *facet2el, const uint32_t *a_words, const uint32_t *b_words,
+                               int bnd_val_a, int bnd_val_b, int use_and, uint32_t *out_words, void *stream);
+int ngsx_elements_with_neighbor_facets(int64_t nf, const int32_t *facet2el, const uint32_t *facet_words,
+                                       int64_t ne, uint32_t *out_words /* zeroed by the callee */, void *stream);
+int ngsx_dofs_of_elements(int64_t n, int32_t nd, const int32_t *table, const uint32_t *a_words,
+                          int64_t ndof, uint32_t *out_words /* zeroed by the callee */, void *stream);
+
+/* ---- ghost penalty: facet-patch matrices ------------------------------------------------------------------------ */
+/* patch matrix of  coef * h^hpow * (u - u.Other()) (v - v.Other())  over both elements of each listed facet patch
+ * (py_tutorials/fictdom_ghostpen.py:105-107); patch_els [np][2]; elmats [np][2nd][2nd] over [dofs(el0) | dofs(el1)]. */
+int ngsx_facetpatch_elmat_h1(const ngsx_mesh *mesh, int fe_order, double coef, int hpow, int64_t npatch,
+                             const int32_t *patch_els, double *elmats, void *stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* NGSX_ABI_H */

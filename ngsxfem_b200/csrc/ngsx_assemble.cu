@@ -1,0 +1,679 @@
+// ngsx_assemble.cu -- (c) cut element matrices / vectors and (d) the fused colour-ordered scatter into CSR.
+//
+// Execution model (B200, 148 SMs): persistent CTAs of 8 warps; ONE WARP PER GROUP of consecutive list entries.
+// A warp walks its group element by element; for each element all 32 lanes cooperate:
+//   * every lane redundantly loads the 4 vertices / level-set values (one broadcast transaction) and derives the
+//     affine geometry, the sign pattern and -- for cut elements -- the sub-simplex decomposition (table driven);
+//   * uncut elements of the requested domain take the constant-rule path: the reference rule is the same on every
+//     such element, so  sum_q w_q dphi_i/dxi_a dphi_j/dxi_b  is a per-CTA shared-memory table contracted with
+//     J^-1 J^-T (same quadrature as the reference, re-associated);
+//   * cut elements stage shape values/gradients of 16 quadrature points at a time in shared memory (lane q computes
+//     point q) and every lane accumulates its 1..4 matrix entries over the staged points;
+//   * sink: either a coalesced store of the dense nd x nd block, or "+=" into the CSR value array through the
+//     precomputed slot map (coalesced int32 reads).  Groups of one colour share no dof and a warp processes its own
+//     group sequentially, so there are no floating-point atomics and the result is bitwise reproducible.
+// HBM-bound: 184 B in + 1600 B CSR read-modify-write per P2 element.
+#include <algorithm>
+#include <cstring>
+#include <vector>
+#include "ngsx_host.cuh"
+
+namespace ngsx {
+
+constexpr int WARPS = 8;          // warps per CTA
+constexpr int QC = 16;            // quadrature points staged per round
+
+struct FormDev { double cm, cs, cn; int pm, ps, pn; };
+
+struct ElmatArgs {
+  ngsx_mesh M;
+  const double *lset;
+  const CutTable *tab;
+  int dt;
+  const double4 *rule_vol; int nr_vol;
+  const double4 *rule_if;  int nr_if;
+  FormDev form;
+  const int32_t *els;          // list of element numbers (NULL: identity)
+  int group;                   // list entries per warp-sequential group
+  int use_fast;                // constant-rule path for uncut elements
+  // sinks
+  double *elmats; int32_t *npts;          // dense
+  const int32_t *slots; double *vals;     // CSR
+};
+
+template <int DIM, int ORDER> struct Smem {
+  static constexpr int ND = H1<DIM, ORDER>::ND;
+  static constexpr int NE = ND * ND;
+  static constexpr int NPAIR = DIM * (DIM + 1) / 2;
+  // offsets in bytes
+  static __host__ __device__ size_t rule_vol() { return 0; }
+  static __host__ __device__ size_t rule_if(int nr_vol) { return (size_t)nr_vol * 32; }
+  static __host__ __device__ size_t tab(int nr_vol, int nr_if) { return (size_t)(nr_vol + nr_if) * 32; }
+  static __host__ __device__ size_t lut(int nr_vol, int nr_if) { return tab(nr_vol, nr_if) + (size_t)(NPAIR + 1) * NE * 8; }
+  static __host__ __device__ size_t stage(int nr_vol, int nr_if) { return lut(nr_vol, nr_if) + 256; }
+  static __host__ __device__ size_t stage_per_warp() { return (size_t)QC * ND * 32 + QC * 8; }
+  static __host__ __device__ size_t total(int nr_vol, int nr_if) { return stage(nr_vol, nr_if) + WARPS * stage_per_warp(); }
+};
+
+template <int DIM>
+__device__ __forceinline__ void load_el(const ngsx_mesh &M, const double *__restrict__ lset, int64_t e, double *ls, double (*p)[DIM]) {
+  int v[4];
+  if constexpr (DIM == 3) {
+    int4 q = __ldg(reinterpret_cast<const int4 *>(M.el2v) + e);
+    v[0] = q.x; v[1] = q.y; v[2] = q.z; v[3] = q.w;
+  } else {
+    const int32_t *q = M.el2v + 3 * e;
+    v[0] = __ldg(q); v[1] = __ldg(q + 1); v[2] = __ldg(q + 2);
+  }
+#pragma unroll
+  for (int k = 0; k <= DIM; k++) {
+    ls[k] = __ldg(lset + v[k]);
+#pragma unroll
+    for (int d = 0; d < DIM; d++) p[k][d] = __ldg(M.vert + (int64_t)v[k] * DIM + d);
+  }
+}
+
+template <int DIM>
+__device__ __forceinline__ void bary_gradients(const ElGeom<DIM> &G, double (*gl)[DIM]) {
+#pragma unroll
+  for (int d = 0; d < DIM; d++) {
+    double s = 0.0;
+#pragma unroll
+    for (int k = 0; k < DIM; k++) { gl[k][d] = G.Jinv[k][d]; s += G.Jinv[k][d]; }
+    gl[DIM][d] = -s;
+  }
+}
+
+// SINK: 0 dense element matrices, 1 CSR read-modify-write
+template <int DIM, int ORDER, int SINK>
+__global__ void __launch_bounds__(WARPS * 32) k_elmat(ElmatArgs A, int64_t first, int64_t count) {
+  using S = Smem<DIM, ORDER>;
+  constexpr int ND = S::ND, NE = S::NE, NPAIR = S::NPAIR, T = (NE + 31) / 32;
+  extern __shared__ __align__(16) unsigned char smem_raw[];
+  double4 *srule_vol = reinterpret_cast<double4 *>(smem_raw + S::rule_vol());
+  double4 *srule_if = reinterpret_cast<double4 *>(smem_raw + S::rule_if(A.nr_vol));
+  double *tab = reinterpret_cast<double *>(smem_raw + S::tab(A.nr_vol, A.nr_if));
+  CutEntry *lut = reinterpret_cast<CutEntry *>(smem_raw + S::lut(A.nr_vol, A.nr_if));
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  unsigned char *wbase = smem_raw + S::stage(A.nr_vol, A.nr_if) + warp * S::stage_per_warp();
+  double4 *stage = reinterpret_cast<double4 *>(wbase);
+  double *facq = reinterpret_cast<double *>(wbase + (size_t)QC * ND * 32);
+
+  // ---- CTA prologue: rules, decomposition table, constant-rule tables --------------------------------------
+  for (int i = threadIdx.x; i < A.nr_vol; i += blockDim.x) srule_vol[i] = A.rule_vol[i];
+  for (int i = threadIdx.x; i < A.nr_if; i += blockDim.x) srule_if[i] = A.rule_if[i];
+  if (threadIdx.x < 16) lut[threadIdx.x] = A.tab->e[DIM - 2][A.dt][threadIdx.x];
+  __syncthreads();
+  const bool fast = A.use_fast && A.dt != IF;
+  if (fast) {
+    double glr[DIM + 1][DIM];                      // reference gradients of the barycentrics
+#pragma unroll
+    for (int k = 0; k <= DIM; k++)
+#pragma unroll
+      for (int d = 0; d < DIM; d++) glr[k][d] = (k == DIM) ? -1.0 : (k == d ? 1.0 : 0.0);
+    for (int idx = threadIdx.x; idx < NE; idx += blockDim.x) {
+      int i = idx / ND, j = idx % ND;
+      double acc[NPAIR + 1];
+#pragma unroll
+      for (int k = 0; k <= NPAIR; k++) acc[k] = 0.0;
+      for (int q = 0; q < A.nr_vol; q++) {
+        double4 r = srule_vol[q];
+        double lam[4] = {r.x, r.y, r.z, 0.0};
+        double last = 1.0;
+#pragma unroll
+        for (int k = 0; k < DIM; k++) last -= lam[k];
+        lam[DIM] = last;
+        double si, sj, gi[DIM], gj[DIM];
+        h1_shape_grad<DIM, ORDER>(i, lam, glr, si, gi);
+        h1_shape_grad<DIM, ORDER>(j, lam, glr, sj, gj);
+        int pr = 0;
+#pragma unroll
+        for (int a = 0; a < DIM; a++)
+#pragma unroll
+          for (int b = a; b < DIM; b++) {
+            acc[pr] += r.w * (a == b ? gi[a] * gj[a] : (gi[a] * gj[b] + gi[b] * gj[a]));
+            pr++;
+          }
+        acc[NPAIR] += r.w * si * sj;
+      }
+#pragma unroll
+      for (int k = 0; k <= NPAIR; k++) tab[k * NE + idx] = acc[k];
+    }
+    __syncthreads();
+  }
+
+  // per-lane matrix entries
+  int ei[T], ej[T];
+#pragma unroll
+  for (int t = 0; t < T; t++) {
+    int idx = lane + 32 * t;
+    ei[t] = idx < NE ? idx / ND : 0;
+    ej[t] = idx < NE ? idx % ND : 0;
+  }
+
+  const int64_t ngroups = (count + A.group - 1) / A.group;
+  const int64_t nwarps = (int64_t)gridDim.x * WARPS;
+  for (int64_t g = (int64_t)blockIdx.x * WARPS + warp; g < ngroups; g += nwarps) {
+    const int64_t kb = first + g * A.group;
+    const int64_t ke = min(kb + (int64_t)A.group, first + count);
+    for (int64_t k = kb; k < ke; k++) {
+      const int64_t e = A.els ? A.els[k] : k;
+      double ls[4], p[DIM + 1][DIM];
+      load_el<DIM>(A.M, A.lset, e, ls, p);
+      int mask;
+      const int dom = sign_test<DIM>(ls, mask);
+      const bool cut = dom == IF;
+      double acc[T];
+#pragma unroll
+      for (int t = 0; t < T; t++) acc[t] = 0.0;
+      int np_used = 0;
+      const bool active = cut || dom == A.dt;
+      if (active) {
+        ElGeom<DIM> G;
+        element_geometry<DIM>(p, G);
+        const double meas = fabs(G.det);
+        double cm = A.form.cm, cs = A.form.cs, cn = A.form.cn;
+        if (A.form.pm | A.form.ps | A.form.pn) {
+          double h = DIM == 2 ? sqrt(meas) : cbrt(meas);           // specialcf.mesh_size = |det J|^(1/dim)
+          cm *= ipow(h, A.form.pm); cs *= ipow(h, A.form.ps); cn *= ipow(h, A.form.pn);
+        }
+        if (!cut && fast) {
+          // ---- constant-rule path -------------------------------------------------------------------------
+          double gs[NPAIR];
+          int pr = 0;
+#pragma unroll
+          for (int a = 0; a < DIM; a++)
+#pragma unroll
+            for (int b = a; b < DIM; b++) {
+              double s = 0.0;
+#pragma unroll
+              for (int d = 0; d < DIM; d++) s += G.Jinv[a][d] * G.Jinv[b][d];
+              gs[pr++] = s;
+            }
+#pragma unroll
+          for (int t = 0; t < T; t++) {
+            int idx = lane + 32 * t;
+            if (idx < NE) {
+              double s = 0.0;
+#pragma unroll
+              for (int q = 0; q < NPAIR; q++) s += gs[q] * tab[q * NE + idx];
+              acc[t] = meas * (cs * s + cm * tab[NPAIR * NE + idx]);
+            }
+          }
+          np_used = A.nr_vol;
+        } else {
+          // ---- quadrature path ----------------------------------------------------------------------------
+          double gl[DIM + 1][DIM];
+          bary_gradients<DIM>(G, gl);
+          double nrm[DIM];
+          double scale = 1.0;
+          {
+            double g2 = 0.0, r2 = 0.0;
+#pragma unroll
+            for (int d = 0; d < DIM; d++) {
+              double v = 0.0;
+#pragma unroll
+              for (int kk = 0; kk <= DIM; kk++) v += ls[kk] * gl[kk][d];
+              nrm[d] = v; g2 += v * v;
+            }
+#pragma unroll
+            for (int kk = 0; kk < DIM; kk++) { double v = ls[kk] - ls[DIM]; r2 += v * v; }
+            double inv = 1.0 / sqrt(g2);
+#pragma unroll
+            for (int d = 0; d < DIM; d++) nrm[d] *= inv;
+            if (cut && A.dt == IF) scale = sqrt(g2) / sqrt(r2);       // |F^-T n_ref|
+          }
+          CutEntry E;
+          if (cut) E = lut[mask]; else { E.ns = 1; E.npt = 0; }
+          const double4 *rule = (cut && A.dt == IF) ? srule_if : srule_vol;
+          const int nr = (cut && A.dt == IF) ? A.nr_if : A.nr_vol;
+          np_used = E.ns * nr;
+          for (int s = 0; s < E.ns; s++) {
+            double P[4][3];
+            double sfac = 1.0;
+            if (cut) {
+              for (int v = 0; v < E.npt; v++) coded_point<DIM>(E.v[s][v], ls, P[v]);
+              sfac = simplex_factor(E.npt, P);
+            }
+            for (int q0 = 0; q0 < nr; q0 += QC) {
+              const int nq = min(QC, nr - q0);
+              if (lane < nq) {
+                double4 r = rule[q0 + lane];
+                double xi[3] = {r.x, r.y, r.z};
+                if (cut) simplex_point(E.npt, P, r, xi);
+                double lam[4] = {xi[0], xi[1], xi[2], 0.0};
+                double last = 1.0;
+#pragma unroll
+                for (int kk = 0; kk < DIM; kk++) last -= lam[kk];
+                lam[DIM] = last;
+#pragma unroll
+                for (int i = 0; i < ND; i++) {
+                  double sv, gv[DIM];
+                  h1_shape_grad<DIM, ORDER>(i, lam, gl, sv, gv);
+                  stage[lane * ND + i] = make_double4(sv, gv[0], gv[1], DIM == 3 ? gv[DIM - 1] : 0.0);
+                }
+                facq[lane] = meas * (r.w * sfac * scale);
+              }
+              __syncwarp();
+              for (int q = 0; q < nq; q++) {
+                const double f = facq[q];
+#pragma unroll
+                for (int t = 0; t < T; t++) {
+                  const double4 bi = stage[q * ND + ei[t]], bj = stage[q * ND + ej[t]];
+                  double gg = bi.y * bj.y + bi.z * bj.z + (DIM == 3 ? bi.w * bj.w : 0.0);
+                  double v = cs * gg + cm * bi.x * bj.x;
+                  if (cn != 0.0) {
+                    double gin = bi.y * nrm[0] + bi.z * nrm[1] + (DIM == 3 ? bi.w * nrm[DIM - 1] : 0.0);
+                    double gjn = bj.y * nrm[0] + bj.z * nrm[1] + (DIM == 3 ? bj.w * nrm[DIM - 1] : 0.0);
+                    v += cn * (gjn * bi.x + gin * bj.x);
+                  }
+                  acc[t] += f * v;
+                }
+              }
+              __syncwarp();
+            }
+          }
+        }
+      }
+      // ---- sink ---------------------------------------------------------------------------------------------
+      if constexpr (SINK == 0) {
+#pragma unroll
+        for (int t = 0; t < T; t++) {
+          int idx = lane + 32 * t;
+          if (idx < NE) A.elmats[k * NE + idx] = acc[t];
+        }
+        if (A.npts && lane == 0) A.npts[k] = np_used;
+      } else {
+        if (active) {
+#pragma unroll
+          for (int t = 0; t < T; t++) {
+            int idx = lane + 32 * t;
+            if (idx < NE) {
+              int32_t sl = __ldg(A.slots + k * NE + idx);
+              A.vals[sl] += acc[t];
+            }
+          }
+        }
+        __syncwarp();          // next element of the group may touch the same CSR entries from another lane
+      }
+    }
+  }
+}
+
+// ---------------------------------------------------------------------------------------------------------------
+// element vectors (SymbolicCutLFI): same staging, lanes < ND accumulate  sum_q fac_q f(x_q) phi_i(x_q)
+// SINK 0: dense elvecs[k][ND]; 1: vec[el2dof_list[k][i]] += (coloured groups)
+// ---------------------------------------------------------------------------------------------------------------
+struct PolyDev2 { int n; double c[NGSX_POLY_MAXTERMS]; int ex[NGSX_POLY_MAXTERMS][3]; };
+
+struct ElvecArgs {
+  ngsx_mesh M;
+  const double *lset;
+  const CutTable *tab;
+  int dt;
+  const double4 *rule_vol; int nr_vol;
+  const double4 *rule_if;  int nr_if;
+  PolyDev2 f;
+  const int32_t *els;
+  int group;
+  double *elvecs; int32_t *npts;
+  const int32_t *el2dof_list; double *vec;
+};
+
+template <int DIM, int ORDER, int SINK>
+__global__ void __launch_bounds__(WARPS * 32) k_elvec(ElvecArgs A, int64_t first, int64_t count) {
+  constexpr int ND = H1<DIM, ORDER>::ND;
+  extern __shared__ __align__(16) unsigned char smem_raw[];
+  double4 *srule_vol = reinterpret_cast<double4 *>(smem_raw);
+  double4 *srule_if = srule_vol + A.nr_vol;
+  CutEntry *lut = reinterpret_cast<CutEntry *>(srule_if + A.nr_if);
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  double *stage = reinterpret_cast<double *>(smem_raw + (size_t)(A.nr_vol + A.nr_if) * 32 + 256) + warp * (32 * ND + 32);
+  double *facq = stage + 32 * ND;
+  for (int i = threadIdx.x; i < A.nr_vol; i += blockDim.x) srule_vol[i] = A.rule_vol[i];
+  for (int i = threadIdx.x; i < A.nr_if; i += blockDim.x) srule_if[i] = A.rule_if[i];
+  if (threadIdx.x < 16) lut[threadIdx.x] = A.tab->e[DIM - 2][A.dt][threadIdx.x];
+  __syncthreads();
+  const int64_t ngroups = (count + A.group - 1) / A.group;
+  const int64_t nwarps = (int64_t)gridDim.x * WARPS;
+  for (int64_t g = (int64_t)blockIdx.x * WARPS + warp; g < ngroups; g += nwarps) {
+    const int64_t kb = first + g * A.group;
+    const int64_t ke = min(kb + (int64_t)A.group, first + count);
+    for (int64_t k = kb; k < ke; k++) {
+      const int64_t e = A.els ? A.els[k] : k;
+      double ls[4], p[DIM + 1][DIM];
+      load_el<DIM>(A.M, A.lset, e, ls, p);
+      int mask;
+      const int dom = sign_test<DIM>(ls, mask);
+      const bool cut = dom == IF;
+      const bool active = cut || dom == A.dt;
+      double acc = 0.0;
+      int np_used = 0;
+      if (active) {
+        ElGeom<DIM> G;
+        element_geometry<DIM>(p, G);
+        const double meas = fabs(G.det);
+        double scale = 1.0;
+        if (cut && A.dt == IF) {
+          double gl[DIM + 1][DIM];
+          bary_gradients<DIM>(G, gl);
+          double g2 = 0.0, r2 = 0.0;
+#pragma unroll
+          for (int d = 0; d < DIM; d++) {
+            double v = 0.0;
+#pragma unroll
+            for (int kk = 0; kk <= DIM; kk++) v += ls[kk] * gl[kk][d];
+            g2 += v * v;
+          }
+#pragma unroll
+          for (int kk = 0; kk < DIM; kk++) { double v = ls[kk] - ls[DIM]; r2 += v * v; }
+          scale = sqrt(g2) / sqrt(r2);
+        }
+        CutEntry E;
+        if (cut) E = lut[mask]; else { E.ns = 1; E.npt = 0; }
+        const double4 *rule = (cut && A.dt == IF) ? srule_if : srule_vol;
+        const int nr = (cut && A.dt == IF) ? A.nr_if : A.nr_vol;
+        np_used = E.ns * nr;
+        for (int s = 0; s < E.ns; s++) {
+          double P[4][3];
+          double sfac = 1.0;
+          if (cut) {
+            for (int v = 0; v < E.npt; v++) coded_point<DIM>(E.v[s][v], ls, P[v]);
+            sfac = simplex_factor(E.npt, P);
+          }
+          for (int q0 = 0; q0 < nr; q0 += 32) {
+            const int nq = min(32, nr - q0);
+            if (lane < nq) {
+              double4 r = rule[q0 + lane];
+              double xi[3] = {r.x, r.y, r.z};
+              if (cut) simplex_point(E.npt, P, r, xi);
+              double lam[4] = {xi[0], xi[1], xi[2], 0.0};
+              double last = 1.0;
+#pragma unroll
+              for (int kk = 0; kk < DIM; kk++) last -= lam[kk];
+              lam[DIM] = last;
+              double x[3] = {0.0, 0.0, 0.0};
+#pragma unroll
+              for (int d = 0; d < DIM; d++) {
+                double v = 0.0;
+#pragma unroll
+                for (int kk = 0; kk <= DIM; kk++) v += lam[kk] * p[kk][d];
+                x[d] = v;
+              }
+              double fx = 0.0;
+              for (int m = 0; m < A.f.n; m++)
+                fx += A.f.c[m] * ipow(x[0], A.f.ex[m][0]) * ipow(x[1], A.f.ex[m][1]) * ipow(x[2], A.f.ex[m][2]);
+#pragma unroll
+              for (int i = 0; i < ND; i++) stage[lane * ND + i] = h1_shape<DIM, ORDER>(i, lam);
+              facq[lane] = meas * (r.w * sfac * scale) * fx;
+            }
+            __syncwarp();
+            if (lane < ND)
+              for (int q = 0; q < nq; q++) acc += facq[q] * stage[q * ND + lane];
+            __syncwarp();
+          }
+        }
+      }
+      if constexpr (SINK == 0) {
+        if (lane < ND) A.elvecs[k * ND + lane] = acc;
+        if (A.npts && lane == 0) A.npts[k] = np_used;
+      } else {
+        if (active && lane < ND) A.vec[A.el2dof_list[k * ND + lane]] += acc;
+        __syncwarp();
+      }
+    }
+  }
+}
+
+// slot map: one thread per (list entry, i, j): binary search of the sorted CSR row
+__global__ void __launch_bounds__(256) k_slot_map(int64_t n, int nd, const int32_t *__restrict__ table, const int64_t *__restrict__ rowptr,
+                                                 const int32_t *__restrict__ colidx, int32_t *__restrict__ slots) {
+  int64_t t = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  int ne = nd * nd;
+  if (t >= n * ne) return;
+  int64_t k = t / ne;
+  int idx = (int)(t % ne);
+  int row = table[k * nd + idx / nd], col = table[k * nd + idx % nd];
+  int64_t lo = rowptr[row], hi = rowptr[row + 1] - 1;
+  while (lo < hi) {
+    int64_t mid = (lo + hi) >> 1;
+    if (colidx[mid] < col) lo = mid + 1; else hi = mid;
+  }
+  slots[t] = (colidx[lo] == col) ? (int32_t)lo : -1;
+}
+
+template <typename K>
+static int configure(K kernel, size_t smem, int sm_count, int64_t nwarp_items, unsigned *grid) {
+  NGSX_CUDA(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  int occ = 0;
+  NGSX_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, kernel, WARPS * 32, smem));
+  if (occ < 1) { set_error("kernel does not fit on an SM"); return NGSX_ERR_CUDA; }
+  int64_t need = (nwarp_items + WARPS - 1) / WARPS;
+  int64_t cap = (int64_t)sm_count * occ;
+  *grid = (unsigned)std::max<int64_t>(1, std::min(need, cap));
+  return NGSX_OK;
+}
+
+static int fill_common(const ngsx_mesh *mesh, const double *lset_v, int fe_order, int dt, int intorder, const DeviceData **dd,
+                       const double4 **rv, int *nv, const double4 **ri, int *ni) {
+  NGSX_REQUIRE(mesh && (mesh->dim == 2 || mesh->dim == 3), "mesh.dim must be 2 or 3");
+  NGSX_REQUIRE(lset_v && mesh->vert && mesh->el2v, "mesh / level-set arrays are NULL");
+  NGSX_REQUIRE(dt >= 0 && dt <= 2, "domain_type must be NEG, POS or IF");
+  if (fe_order < 1 || fe_order > 2) {
+    set_error("H1 order outside the CUDA path (supported: 1, 2); no CPU fallback");
+    return NGSX_ERR_UNSUPPORTED;
+  }
+  *dd = device_data();
+  if (!*dd) return NGSX_ERR_CUDA;
+  if (!rule_lookup(*dd, mesh->dim, intorder, rv, nv) || !rule_lookup(*dd, mesh->dim - 1, intorder, ri, ni)) {
+    set_error("integration order beyond the tabulated reference rules");
+    return NGSX_ERR_UNSUPPORTED;
+  }
+  return NGSX_OK;
+}
+
+template <int DIM, int ORDER, int SINK>
+static int launch_elmat(const ElmatArgs &A, int sm_count, int ncolors, const int64_t *h_color_ptr, int64_t nlist, cudaStream_t st) {
+  using S = Smem<DIM, ORDER>;
+  size_t smem = S::total(A.nr_vol, A.nr_if);
+  auto kern = k_elmat<DIM, ORDER, SINK>;
+  for (int c = 0; c < ncolors; c++) {
+    int64_t first = h_color_ptr ? h_color_ptr[c] : 0;
+    int64_t count = h_color_ptr ? h_color_ptr[c + 1] - h_color_ptr[c] : nlist;
+    if (count <= 0) continue;
+    unsigned grid;
+    if (int rc = configure(kern, smem, sm_count, (count + A.group - 1) / A.group, &grid)) return rc;
+    kern<<<grid, WARPS * 32, smem, st>>>(A, first, count);
+    NGSX_LAUNCH_CHECK();
+  }
+  return NGSX_OK;
+}
+
+template <int SINK>
+static int dispatch_elmat(const ElmatArgs &A, int fe_order, int sm_count, int ncolors, const int64_t *h_color_ptr, int64_t nlist, cudaStream_t st) {
+  int key = A.M.dim * 10 + fe_order;
+  switch (key) {
+    case 21: return launch_elmat<2, 1, SINK>(A, sm_count, ncolors, h_color_ptr, nlist, st);
+    case 22: return launch_elmat<2, 2, SINK>(A, sm_count, ncolors, h_color_ptr, nlist, st);
+    case 31: return launch_elmat<3, 1, SINK>(A, sm_count, ncolors, h_color_ptr, nlist, st);
+    case 32: return launch_elmat<3, 2, SINK>(A, sm_count, ncolors, h_color_ptr, nlist, st);
+  }
+  set_error("unsupported (dim, order)");
+  return NGSX_ERR_UNSUPPORTED;
+}
+
+template <int DIM, int ORDER, int SINK>
+static int launch_elvec(const ElvecArgs &A, int sm_count, int ncolors, const int64_t *h_color_ptr, int64_t nlist, cudaStream_t st) {
+  constexpr int ND = H1<DIM, ORDER>::ND;
+  size_t smem = (size_t)(A.nr_vol + A.nr_if) * 32 + 256 + (size_t)WARPS * (32 * ND + 32) * 8;
+  auto kern = k_elvec<DIM, ORDER, SINK>;
+  for (int c = 0; c < ncolors; c++) {
+    int64_t first = h_color_ptr ? h_color_ptr[c] : 0;
+    int64_t count = h_color_ptr ? h_color_ptr[c + 1] - h_color_ptr[c] : nlist;
+    if (count <= 0) continue;
+    unsigned grid;
+    if (int rc = configure(kern, smem, sm_count, (count + A.group - 1) / A.group, &grid)) return rc;
+    kern<<<grid, WARPS * 32, smem, st>>>(A, first, count);
+    NGSX_LAUNCH_CHECK();
+  }
+  return NGSX_OK;
+}
+
+template <int SINK>
+static int dispatch_elvec(const ElvecArgs &A, int fe_order, int sm_count, int ncolors, const int64_t *h_color_ptr, int64_t nlist, cudaStream_t st) {
+  int key = A.M.dim * 10 + fe_order;
+  switch (key) {
+    case 21: return launch_elvec<2, 1, SINK>(A, sm_count, ncolors, h_color_ptr, nlist, st);
+    case 22: return launch_elvec<2, 2, SINK>(A, sm_count, ncolors, h_color_ptr, nlist, st);
+    case 31: return launch_elvec<3, 1, SINK>(A, sm_count, ncolors, h_color_ptr, nlist, st);
+    case 32: return launch_elvec<3, 2, SINK>(A, sm_count, ncolors, h_color_ptr, nlist, st);
+  }
+  set_error("unsupported (dim, order)");
+  return NGSX_ERR_UNSUPPORTED;
+}
+
+static int g_use_fast = 1;
+
+}  // namespace ngsx
+
+using namespace ngsx;
+
+extern "C" {
+
+// test hook: 0 disables the constant-rule path so both paths can be compared on the GPU
+void ngsx_debug_set_fast_path(int on) { g_use_fast = on; }
+
+static void fill_form(const ngsx_form_h1 *f, FormDev &d) {
+  d.cm = f->c_mass; d.cs = f->c_stiff; d.cn = f->c_nitsche;
+  d.pm = f->hpow_mass; d.ps = f->hpow_stiff; d.pn = f->hpow_nitsche;
+}
+
+int ngsx_elmat_h1(const ngsx_mesh *mesh, const double *lset_v, int fe_order, int dt, int intorder, const ngsx_form_h1 *h_form,
+                  int64_t nlist, const int32_t *els, double *elmats, int32_t *npts, void *stream) {
+  const DeviceData *dd; const double4 *rv, *ri; int nv, ni;
+  NGSX_REQUIRE(h_form && (nlist == 0 || elmats) && nlist >= 0, "elmat_h1: bad arguments");
+  if (int rc = fill_common(mesh, lset_v, fe_order, dt, intorder, &dd, &rv, &nv, &ri, &ni)) return rc;
+  if (nlist == 0) return NGSX_OK;
+  ElmatArgs A{};
+  A.M = *mesh; A.lset = lset_v; A.tab = dd->cut_table; A.dt = dt;
+  A.rule_vol = rv; A.nr_vol = nv; A.rule_if = ri; A.nr_if = ni;
+  fill_form(h_form, A.form);
+  A.els = els; A.group = 1; A.use_fast = g_use_fast && h_form->c_nitsche == 0.0;
+  A.elmats = elmats; A.npts = npts;
+  return dispatch_elmat<0>(A, fe_order, dd->sm_count, 1, nullptr, nlist, as_stream(stream));
+}
+
+int ngsx_assemble_csr_h1(const ngsx_mesh *mesh, const double *lset_v, int fe_order, int dt, int intorder,
+                         const ngsx_form_h1 *h_form, int64_t nlist, const int32_t *els, const int32_t *slots,
+                         int32_t ncolors, const int64_t *h_color_ptr, int32_t group, double *vals, void *stream) {
+  const DeviceData *dd; const double4 *rv, *ri; int nv, ni;
+  NGSX_REQUIRE(h_form && nlist >= 0 && ncolors >= 0 && group >= 1 && h_color_ptr, "assemble_csr_h1: bad arguments");
+  NGSX_REQUIRE(nlist == 0 || (slots && vals), "assemble_csr_h1: slots / vals are NULL");
+  if (int rc = fill_common(mesh, lset_v, fe_order, dt, intorder, &dd, &rv, &nv, &ri, &ni)) return rc;
+  if (nlist == 0) return NGSX_OK;
+  ElmatArgs A{};
+  A.M = *mesh; A.lset = lset_v; A.tab = dd->cut_table; A.dt = dt;
+  A.rule_vol = rv; A.nr_vol = nv; A.rule_if = ri; A.nr_if = ni;
+  fill_form(h_form, A.form);
+  A.els = els; A.group = group; A.use_fast = g_use_fast && h_form->c_nitsche == 0.0;
+  A.slots = slots; A.vals = vals;
+  return dispatch_elmat<1>(A, fe_order, dd->sm_count, ncolors, h_color_ptr, nlist, as_stream(stream));
+}
+
+static int fill_poly(const ngsx_poly *f, PolyDev2 &d) {
+  NGSX_REQUIRE(f && f->nterms >= 0 && f->nterms <= NGSX_POLY_MAXTERMS, "polynomial: bad number of terms");
+  d.n = f->nterms;
+  for (int m = 0; m < d.n; m++) { d.c[m] = f->coef[m]; for (int k = 0; k < 3; k++) d.ex[m][k] = f->ex[m][k]; }
+  return NGSX_OK;
+}
+
+int ngsx_elvec_h1(const ngsx_mesh *mesh, const double *lset_v, int fe_order, int dt, int intorder, const ngsx_poly *h_f,
+                  int64_t nlist, const int32_t *els, double *elvecs, int32_t *npts, void *stream) {
+  const DeviceData *dd; const double4 *rv, *ri; int nv, ni;
+  NGSX_REQUIRE((nlist == 0 || elvecs) && nlist >= 0, "elvec_h1: bad arguments");
+  if (int rc = fill_common(mesh, lset_v, fe_order, dt, intorder, &dd, &rv, &nv, &ri, &ni)) return rc;
+  ElvecArgs A{};
+  if (int rc = fill_poly(h_f, A.f)) return rc;
+  if (nlist == 0) return NGSX_OK;
+  A.M = *mesh; A.lset = lset_v; A.tab = dd->cut_table; A.dt = dt;
+  A.rule_vol = rv; A.nr_vol = nv; A.rule_if = ri; A.nr_if = ni;
+  A.els = els; A.group = 1; A.elvecs = elvecs; A.npts = npts;
+  return dispatch_elvec<0>(A, fe_order, dd->sm_count, 1, nullptr, nlist, as_stream(stream));
+}
+
+int ngsx_assemble_vec_h1(const ngsx_mesh *mesh, const double *lset_v, int fe_order, int dt, int intorder,
+                         const ngsx_poly *h_f, int64_t nlist, const int32_t *els, const int32_t *el2dof_list,
+                         int32_t ncolors, const int64_t *h_color_ptr, int32_t group, double *vec, void *stream) {
+  const DeviceData *dd; const double4 *rv, *ri; int nv, ni;
+  NGSX_REQUIRE(nlist >= 0 && ncolors >= 0 && group >= 1 && h_color_ptr, "assemble_vec_h1: bad arguments");
+  NGSX_REQUIRE(nlist == 0 || (el2dof_list && vec), "assemble_vec_h1: el2dof_list / vec are NULL");
+  if (int rc = fill_common(mesh, lset_v, fe_order, dt, intorder, &dd, &rv, &nv, &ri, &ni)) return rc;
+  ElvecArgs A{};
+  if (int rc = fill_poly(h_f, A.f)) return rc;
+  if (nlist == 0) return NGSX_OK;
+  A.M = *mesh; A.lset = lset_v; A.tab = dd->cut_table; A.dt = dt;
+  A.rule_vol = rv; A.nr_vol = nv; A.rule_if = ri; A.nr_if = ni;
+  A.els = els; A.group = group; A.el2dof_list = el2dof_list; A.vec = vec;
+  return dispatch_elvec<1>(A, fe_order, dd->sm_count, ncolors, h_color_ptr, nlist, as_stream(stream));
+}
+
+int ngsx_slot_map(int64_t n, int32_t nd, const int32_t *table, const int64_t *rowptr, const int32_t *colidx,
+                  int32_t *slots, void *stream) {
+  NGSX_REQUIRE(n >= 0 && nd > 0 && (n == 0 || (table && rowptr && colidx && slots)), "slot_map: bad arguments");
+  if (n == 0) return NGSX_OK;
+  int64_t tot = n * nd * nd;
+  k_slot_map<<<(unsigned)((tot + 255) / 256), 256, 0, as_stream(stream)>>>(n, nd, table, rowptr, colidx, slots);
+  NGSX_LAUNCH_CHECK();
+  return NGSX_OK;
+}
+
+// HOST: greedy colouring of groups (see header).  Colours are bits in per-dof masks, 64 at a time.
+int ngsx_color_groups(int64_t n, int32_t nd, const int32_t *h_table, int64_t ndof, int32_t group,
+                      int64_t *h_perm, int64_t *h_color_ptr, int32_t cap_colors, int32_t *h_ncolors) {
+  NGSX_REQUIRE(n >= 0 && nd > 0 && group >= 1 && ndof >= 0 && h_ncolors && (n == 0 || (h_table && h_perm && h_color_ptr)),
+               "color_groups: bad arguments");
+  *h_ncolors = 0;
+  if (n == 0) { if (h_color_ptr) h_color_ptr[0] = 0; return NGSX_OK; }
+  const int64_t ng = (n + group - 1) / group;
+  std::vector<int32_t> color(ng, -1);
+  std::vector<uint64_t> mask(ndof);
+  int64_t left = ng;
+  int base = 0, maxcol = -1;
+  while (left > 0) {                                  // sweep: 64 colours per pass over the still-uncoloured groups
+    std::fill(mask.begin(), mask.end(), 0ULL);
+    for (int64_t g = 0; g < ng; g++) {
+      if (color[g] >= 0) continue;
+      const int64_t kb = g * group, ke = std::min<int64_t>(kb + group, n);
+      uint64_t used = 0;
+      for (int64_t t = kb * nd; t < ke * nd; t++) used |= mask[h_table[t]];
+      if (~used == 0ULL) continue;                    // all 64 colours of this sweep taken: next sweep
+      int c = __builtin_ctzll(~used);
+      color[g] = base + c;
+      maxcol = std::max(maxcol, base + c);
+      left--;
+      const uint64_t bit = 1ULL << c;
+      for (int64_t t = kb * nd; t < ke * nd; t++) mask[h_table[t]] |= bit;
+    }
+    base += 64;
+  }
+  const int nc = maxcol + 1;
+  if (nc > cap_colors) { set_error("color_groups: more colours than the caller's capacity"); return NGSX_ERR_CAPACITY; }
+  std::vector<int64_t> cnt(nc + 1, 0);
+  for (int64_t g = 0; g < ng; g++) cnt[color[g] + 1] += std::min<int64_t>(group, n - g * group);
+  for (int c = 0; c < nc; c++) cnt[c + 1] += cnt[c];
+  for (int c = 0; c <= nc; c++) h_color_ptr[c] = cnt[c];
+  std::vector<int64_t> pos(cnt.begin(), cnt.end() - 1);
+  // within a colour, full groups first so that every warp's [kb, kb+group) window is one original group
+  for (int pass = 0; pass < 2; pass++)
+    for (int64_t g = 0; g < ng; g++) {
+      const int64_t kb = g * group, ke = std::min<int64_t>(kb + group, n);
+      const bool full = (ke - kb) == group;
+      if (full != (pass == 0)) continue;
+      int64_t &p = pos[color[g]];
+      for (int64_t k = kb; k < ke; k++) h_perm[p++] = k;
+    }
+  *h_ncolors = nc;
+  return NGSX_OK;
+}
+
+}  // extern "C"

@@ -1,0 +1,678 @@
+// ngsx_core.cu -- library plumbing, InterpolateToP1, CutInfo classification, straight-cut rule emission, Integrate.
+// Hand-written CUDA for sm_100a; HBM-bound integer/FP64 streaming kernels (one thread per element, warp ballots
+// for bit arrays, one warp per cut simplex for rule emission).
+#include <cub/cub.cuh>
+#include <cstring>
+#include <mutex>
+#include <vector>
+#include "ngsx_host.cuh"
+#include "rule_tables.h"
+
+namespace ngsx {
+
+// =============================================================================================================
+// host plumbing
+// =============================================================================================================
+static thread_local std::string t_err;
+std::atomic<int64_t> g_launches{0};
+void set_error(const std::string &msg) { t_err = msg; }
+
+// ---- decomposition table: replay of LevelsetCutSimplex::Decompose (cutint/straightcutrule.cpp:131-196) on symbols
+static void build_cut_entry(int dim, int dt, int mask, CutEntry &E) {
+  memset(&E, 0, sizeof E);
+  int nv = dim + 1;
+  bool pos[4] = {false, false, false, false};
+  for (int k = 0; k < nv; k++) pos[k] = (mask >> k) & 1;
+  uint8_t cuts[6];
+  int nc = 0;
+  for (int i = 0; i < nv; i++)                       // CalcIFPolytopEUsingLset: i<j loop, ">= 0" differs (:53-60)
+    for (int j = i + 1; j < nv; j++)
+      if (pos[i] != pos[j]) cuts[nc++] = uint8_t((i << 4) | j);
+  if (nc == 0) return;
+  auto V = [](int k) { return uint8_t((k << 4) | k); };
+  if (dt == IF) {
+    E.npt = uint8_t(dim);
+    if (nc == dim) {                                 // :139
+      E.ns = 1;
+      for (int k = 0; k < nc; k++) E.v[0][k] = cuts[k];
+    } else if (nc == 4 && dim == 3) {                // :140-143
+      E.ns = 2;
+      E.v[0][0] = cuts[0]; E.v[0][1] = cuts[1]; E.v[0][2] = cuts[3];
+      E.v[1][0] = cuts[0]; E.v[1][1] = cuts[2]; E.v[1][2] = cuts[3];
+    }
+    return;
+  }
+  E.npt = uint8_t(dim + 1);
+  int rel[4], nrel = 0;
+  for (int k = 0; k < nv; k++)
+    if ((dt == POS && pos[k]) || (dt == NEG && !pos[k])) rel[nrel++] = k;
+  if (nrel == 1) {                                   // :156-160  {cuts..., v}
+    E.ns = 1;
+    for (int k = 0; k < nc; k++) E.v[0][k] = cuts[k];
+    E.v[0][nc] = V(rel[0]);
+  } else if (nrel == 2 && dim == 2) {                // :161-168
+    E.ns = 2;
+    E.v[0][0] = V(rel[0]); E.v[0][1] = V(rel[1]); E.v[0][2] = cuts[1];
+    E.v[1][0] = cuts[0];   E.v[1][1] = cuts[1];   E.v[1][2] = V(rel[0]);
+  } else if (nrel == 2 && dim == 3) {                // :169-178
+    E.ns = 3;
+    E.v[0][0] = V(rel[1]); E.v[0][1] = cuts[1];   E.v[0][2] = cuts[2]; E.v[0][3] = cuts[3];
+    E.v[1][0] = V(rel[0]); E.v[1][1] = V(rel[1]); E.v[1][2] = cuts[1]; E.v[1][3] = cuts[2];
+    E.v[2][0] = cuts[0];   E.v[2][1] = cuts[1];   E.v[2][2] = cuts[2]; E.v[2][3] = V(rel[0]);
+  } else if (nrel == 3 && dim == 3) {                // :179-188
+    E.ns = 3;
+    E.v[0][0] = cuts[0];   E.v[0][1] = cuts[1];   E.v[0][2] = cuts[2];   E.v[0][3] = V(rel[2]);
+    E.v[1][0] = V(rel[0]); E.v[1][1] = V(rel[1]); E.v[1][2] = V(rel[2]); E.v[1][3] = cuts[1];
+    E.v[2][0] = cuts[0];   E.v[2][1] = cuts[1];   E.v[2][2] = V(rel[0]); E.v[2][3] = V(rel[2]);
+  }
+}
+
+static std::mutex g_dd_mutex;
+static DeviceData g_dd[64];
+static bool g_dd_ready[64];
+static int g_rule_base[4];     // start of the rules of simplex dimension 0..3 inside DeviceData::rules
+
+const DeviceData *device_data() {
+  int dev = 0;
+  if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) { set_error("cudaGetDevice failed"); return nullptr; }
+  std::lock_guard<std::mutex> lock(g_dd_mutex);
+  if (g_dd_ready[dev]) return &g_dd[dev];
+  std::vector<double4> all;
+  g_rule_base[0] = 0;
+  all.push_back(make_double4(0, 0, 0, 1.0));                        // ET_POINT rule
+  auto push = [&](const double (*d)[4], int n) { for (int i = 0; i < n; i++) all.push_back(make_double4(d[i][0], d[i][1], d[i][2], d[i][3])); };
+  g_rule_base[1] = (int)all.size(); push(NGSX_RULE_SEGM_DATA, NGSX_RULE_SEGM_NPTS);
+  g_rule_base[2] = (int)all.size(); push(NGSX_RULE_TRIG_DATA, NGSX_RULE_TRIG_NPTS);
+  g_rule_base[3] = (int)all.size(); push(NGSX_RULE_TET_DATA, NGSX_RULE_TET_NPTS);
+  CutTable tab;
+  for (int dim = 2; dim <= 3; dim++)
+    for (int dt = 0; dt < 3; dt++)
+      for (int mask = 0; mask < 16; mask++) build_cut_entry(dim, dt, mask, tab.e[dim - 2][dt][mask]);
+  DeviceData dd;
+  if (cudaMalloc(&dd.rules, all.size() * sizeof(double4)) != cudaSuccess ||
+      cudaMalloc(&dd.cut_table, sizeof(CutTable)) != cudaSuccess ||
+      cudaMemcpy(dd.rules, all.data(), all.size() * sizeof(double4), cudaMemcpyHostToDevice) != cudaSuccess ||
+      cudaMemcpy(dd.cut_table, &tab, sizeof(CutTable), cudaMemcpyHostToDevice) != cudaSuccess ||
+      cudaDeviceGetAttribute(&dd.sm_count, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess) {
+    set_error(std::string("device_data: ") + cudaGetErrorString(cudaGetLastError()));
+    return nullptr;
+  }
+  g_dd[dev] = dd;
+  g_dd_ready[dev] = true;
+  return &g_dd[dev];
+}
+
+bool rule_lookup(const DeviceData *dd, int sdim, int order, const double4 **ptr, int *n) {
+  if (order < 0) order = 0;
+  const int *offs = nullptr;
+  int maxo = 0;
+  switch (sdim) {
+    case 0: *ptr = dd->rules; *n = 1; return true;
+    case 1: offs = NGSX_RULE_SEGM_OFFS; maxo = NGSX_RULE_SEGM_MAXORDER; break;
+    case 2: offs = NGSX_RULE_TRIG_OFFS; maxo = NGSX_RULE_TRIG_MAXORDER; break;
+    case 3: offs = NGSX_RULE_TET_OFFS; maxo = NGSX_RULE_TET_MAXORDER; break;
+    default: return false;
+  }
+  if (order > maxo) return false;
+  *ptr = dd->rules + g_rule_base[sdim] + offs[order];
+  *n = offs[order + 1] - offs[order];
+  return true;
+}
+
+static int check_mesh(const ngsx_mesh *m) {
+  NGSX_REQUIRE(m != nullptr, "mesh is NULL");
+  NGSX_REQUIRE(m->dim == 2 || m->dim == 3, "mesh.dim must be 2 (triangles) or 3 (tetrahedra)");
+  NGSX_REQUIRE(m->ne >= 0 && m->nv >= 0, "negative mesh size");
+  NGSX_REQUIRE(m->ne == 0 || (m->vert && m->el2v), "mesh arrays are NULL");
+  return NGSX_OK;
+}
+
+// =============================================================================================================
+// kernels
+// =============================================================================================================
+template <int DIM>
+__device__ __forceinline__ void load_element(const ngsx_mesh &M, const double *__restrict__ lset, int64_t e,
+                                             int *v, double *ls, double (*p)[DIM]) {
+  if constexpr (DIM == 3) {
+    int4 q = __ldg(reinterpret_cast<const int4 *>(M.el2v) + e);
+    v[0] = q.x; v[1] = q.y; v[2] = q.z; v[3] = q.w;
+  } else {
+    const int32_t *q = M.el2v + 3 * e;
+    v[0] = __ldg(q); v[1] = __ldg(q + 1); v[2] = __ldg(q + 2);
+  }
+#pragma unroll
+  for (int k = 0; k <= DIM; k++) {
+    ls[k] = __ldg(lset + v[k]);
+    if (p) {
+#pragma unroll
+      for (int d = 0; d < DIM; d++) p[k][d] = __ldg(M.vert + (int64_t)v[k] * DIM + d);
+    }
+  }
+}
+
+__global__ void k_clamp(int64_t n, const double *__restrict__ in, double eps, double *__restrict__ out) {
+  int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  double v = in[i];
+  if (fabs(v) < eps) v = eps;
+  out[i] = v;
+}
+
+struct LsetParams { double p[8]; };
+
+__global__ void k_lset_cf(int dim, int64_t nv, const double *__restrict__ vert, int kind, LsetParams P, double eps,
+                          double *__restrict__ out) {
+  int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= nv) return;
+  double x = vert[i * dim], y = vert[i * dim + 1], z = dim == 3 ? vert[i * dim + 2] : 0.0;
+  double v;
+  if (kind == NGSX_LSET_AFFINE) v = P.p[0] + P.p[1] * x + P.p[2] * y + P.p[3] * z;
+  else {
+    double dx = x - P.p[0], dy = y - P.p[1], dz = (dim == 3 && kind != NGSX_LSET_CYLZ) ? z - P.p[2] : 0.0;
+    double r = sqrt(dx * dx + dy * dy + dz * dz);
+    v = (kind == NGSX_LSET_RING) ? fabs(r - P.p[3]) - P.p[4] : r - P.p[3];
+  }
+  if (fabs(v) < eps) v = eps;
+  out[i] = v;
+}
+
+// sum over the sub-simplices of (dt) of the measure factor: the order-0 part volume divided by the rule weight
+template <int DIM>
+__device__ __forceinline__ double part_factor(const CutEntry &E, const double *ls) {
+  double s = 0.0;
+  for (int k = 0; k < E.ns; k++) {
+    double P[4][3];
+    for (int v = 0; v < E.npt; v++) coded_point<DIM>(E.v[k][v], ls, P[v]);
+    s += simplex_factor(E.npt, P);
+  }
+  return s;
+}
+
+// (a) one thread per element; one warp = one 32-bit word of every bit array (ballot, no atomics)
+template <int DIM>
+__global__ void __launch_bounds__(256) k_classify(ngsx_mesh M, const double *__restrict__ lset, const CutTable *__restrict__ tab,
+                                                 uint32_t *__restrict__ words, int64_t nwords, int8_t *__restrict__ dom_out,
+                                                 double *__restrict__ ratio, unsigned long long *__restrict__ err) {
+  __shared__ CutEntry lut[2][16];
+  for (int i = threadIdx.x; i < 32; i += blockDim.x) lut[i / 16][i % 16] = tab->e[DIM - 2][i / 16][i % 16];
+  __syncthreads();
+  int64_t e = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  int dom = -2;                                        // -2: beyond ne
+  if (e < M.ne) {
+    int v[4], mask;
+    double ls[4];
+    load_element<DIM>(M, lset, e, v, ls, (double(*)[DIM]) nullptr);
+    dom = sign_test<DIM>(ls, mask);
+    if (ratio) {
+      double r = dom == NEG ? 1.0 : 0.0;
+      if (dom == IF) {                                 // xfem/cutinfo.cpp:79-91 (the common rule weight cancels)
+        double vn = part_factor<DIM>(lut[NEG][mask], ls), vp = part_factor<DIM>(lut[POS][mask], ls);
+        r = vn / (vn + vp);
+      }
+      if (dom == -1) r = nan("");
+      ratio[e] = r;
+    }
+    if (dom_out) dom_out[e] = (int8_t)dom;
+    if (dom == -1 && err) {
+      atomicAdd(&err[0], 1ULL);
+      atomicMin(reinterpret_cast<long long *>(&err[1]), (long long)e);
+    }
+  }
+  if (words) {
+    unsigned bn = __ballot_sync(0xffffffffu, dom == NEG), bp = __ballot_sync(0xffffffffu, dom == POS);
+    unsigned bi = __ballot_sync(0xffffffffu, dom == IF), ba = __ballot_sync(0xffffffffu, dom != -2);
+    int64_t w = e >> 5;
+    if ((threadIdx.x & 31) == 0 && w < nwords) {
+      words[NGSX_CDOM_NO * nwords + w] = 0u;
+      words[NGSX_CDOM_NEG * nwords + w] = bn;
+      words[NGSX_CDOM_POS * nwords + w] = bp;
+      words[NGSX_CDOM_UNCUT * nwords + w] = bn | bp;
+      words[NGSX_CDOM_IF * nwords + w] = bi;
+      words[NGSX_CDOM_HASNEG * nwords + w] = bn | bi;
+      words[NGSX_CDOM_HASPOS * nwords + w] = bp | bi;
+      words[NGSX_CDOM_ANY * nwords + w] = ba;
+    }
+  }
+}
+
+__global__ void k_node_marks(int64_t ne, int npe, const int32_t *__restrict__ el2node, const int8_t *__restrict__ dom,
+                             const double *__restrict__ ratio, int cell_mode, uint32_t *__restrict__ cut_nb, int32_t *__restrict__ dom_of_node) {
+  int64_t e = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (e >= ne) return;
+  int d = dom[e];
+  if (cell_mode) {
+    if (d == IF && cut_nb) atomicOr(&cut_nb[e >> 5], 1u << (e & 31));
+    if ((d == NEG || d == POS) && dom_of_node) dom_of_node[e] = ratio[e] > 0.5 ? NEG : POS;
+    return;
+  }
+  for (int k = 0; k < npe; k++) {
+    int n = el2node[e * npe + k];
+    if (d == IF && cut_nb) atomicOr(&cut_nb[n >> 5], 1u << (n & 31));
+    if ((d == NEG || d == POS) && dom_of_node) atomicMin(&dom_of_node[n], d);   // integer atomic: deterministic
+  }
+}
+
+// (b) rule sizes.  uncut: |static rule| if the element lies in dt else 0; cut: ns * |plain rule|
+template <int DIM>
+__global__ void __launch_bounds__(256) k_rule_count(ngsx_mesh M, const double *__restrict__ lset, const CutTable *__restrict__ tab, int dt,
+                                                   int nr_vol, int nr_if, int32_t *__restrict__ npts, unsigned long long *__restrict__ err) {
+  __shared__ uint8_t ns_lut[16];
+  if (threadIdx.x < 16) ns_lut[threadIdx.x] = tab->e[DIM - 2][dt][threadIdx.x].ns;
+  __syncthreads();
+  int64_t e = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (e >= M.ne) return;
+  int v[4], mask;
+  double ls[4];
+  load_element<DIM>(M, lset, e, v, ls, (double(*)[DIM]) nullptr);
+  int dom = sign_test<DIM>(ls, mask);
+  int n = 0;
+  if (dom == IF) n = ns_lut[mask] * (dt == IF ? nr_if : nr_vol);
+  else if (dom == dt) n = nr_vol;
+  if (dom == -1 && err) {
+    atomicAdd(&err[0], 1ULL);
+    atomicMin(reinterpret_cast<long long *>(&err[1]), (long long)e);
+  }
+  npts[e] = n;
+}
+
+// interface weight factor |F^-T n_ref| (TransformQuadUntrafoToIRInterface, straightcutrule.cpp:558-576)
+template <int DIM>
+__device__ __forceinline__ double interface_scale(const ElGeom<DIM> &G, const double *ls) {
+  double g[DIM], n2 = 0.0;
+#pragma unroll
+  for (int k = 0; k < DIM; k++) { g[k] = ls[k] - ls[DIM]; n2 += g[k] * g[k]; }
+  double inv = 1.0 / sqrt(n2), s2 = 0.0;
+#pragma unroll
+  for (int r = 0; r < DIM; r++) {
+    double v = 0.0;
+#pragma unroll
+    for (int k = 0; k < DIM; k++) v += G.Jinv[k][r] * (g[k] * inv);
+    s2 += v * v;
+  }
+  return sqrt(s2);
+}
+
+// (b) emission: one warp per element, lanes stride over the points; order = sub-simplex by sub-simplex, table order inside
+template <int DIM>
+__global__ void __launch_bounds__(256) k_rule_fill(ngsx_mesh M, const double *__restrict__ lset, const CutTable *__restrict__ tab, int dt,
+                                                  const double4 *__restrict__ rule_vol, int nr_vol, const double4 *__restrict__ rule_if, int nr_if,
+                                                  int transform_if, int emit_uncut, const int64_t *__restrict__ offs,
+                                                  double *__restrict__ pts3, double *__restrict__ wts) {
+  __shared__ CutEntry lut[16];
+  if (threadIdx.x < 16) lut[threadIdx.x] = tab->e[DIM - 2][dt][threadIdx.x];
+  __syncthreads();
+  int lane = threadIdx.x & 31;
+  int64_t e = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  if (e >= M.ne) return;
+  int v[4], mask;
+  double ls[4], p[DIM + 1][DIM];
+  load_element<DIM>(M, lset, e, v, ls, p);
+  int dom = sign_test<DIM>(ls, mask);
+  int64_t o = offs[e];
+  if (dom != IF) {
+    if (dom != dt || !emit_uncut) return;
+    for (int q = lane; q < nr_vol; q += 32) {
+      double4 r = rule_vol[q];
+      pts3[3 * (o + q)] = r.x; pts3[3 * (o + q) + 1] = r.y; pts3[3 * (o + q) + 2] = r.z;
+      wts[o + q] = r.w;
+    }
+    return;
+  }
+  const CutEntry E = lut[mask];
+  const double4 *rule = dt == IF ? rule_if : rule_vol;
+  int nr = dt == IF ? nr_if : nr_vol;
+  double scale = 1.0;
+  if (dt == IF && transform_if) {
+    ElGeom<DIM> G;
+    element_geometry<DIM>(p, G);
+    scale = interface_scale<DIM>(G, ls);
+  }
+  for (int s = 0; s < E.ns; s++) {
+    double P[4][3];
+    for (int k = 0; k < E.npt; k++) coded_point<DIM>(E.v[s][k], ls, P[k]);
+    double fac = simplex_factor(E.npt, P);
+    for (int q = lane; q < nr; q += 32) {
+      double4 r = rule[q];
+      double x[3];
+      simplex_point(E.npt, P, r, x);
+      int64_t t = o + s * nr + q;
+      pts3[3 * t] = x[0]; pts3[3 * t + 1] = x[1]; pts3[3 * t + 2] = x[2];
+      wts[t] = r.w * fac * scale;
+    }
+  }
+}
+
+struct PolyDev { int n; double c[NGSX_POLY_MAXTERMS]; int ex[NGSX_POLY_MAXTERMS][3]; };
+
+__device__ __forceinline__ double eval_poly(const PolyDev &f, const double *x) {
+  double s = 0.0;
+  for (int m = 0; m < f.n; m++) s += f.c[m] * ipow(x[0], f.ex[m][0]) * ipow(x[1], f.ex[m][1]) * ipow(x[2], f.ex[m][2]);
+  return s;
+}
+
+template <int DIM>
+__device__ __forceinline__ void map_point(const double (*p)[DIM], const double *xi, double *x) {
+  double lam_last = 1.0;
+#pragma unroll
+  for (int k = 0; k < DIM; k++) lam_last -= xi[k];
+#pragma unroll
+  for (int d = 0; d < 3; d++) x[d] = 0.0;
+#pragma unroll
+  for (int d = 0; d < DIM; d++) {
+    double v = lam_last * p[DIM][d];
+#pragma unroll
+    for (int k = 0; k < DIM; k++) v += xi[k] * p[k][d];
+    x[d] = v;
+  }
+}
+
+// Integrate: one thread per element, fixed-shape block tree -> one partial per block
+template <int DIM>
+__global__ void __launch_bounds__(256) k_integrate(ngsx_mesh M, const double *__restrict__ lset, const CutTable *__restrict__ tab, int dt,
+                                                  const double4 *__restrict__ rule_vol, int nr_vol, const double4 *__restrict__ rule_if, int nr_if,
+                                                  PolyDev f, double *__restrict__ partial) {
+  extern __shared__ double4 srule[];               // nr_vol + nr_if
+  __shared__ CutEntry lut[16];
+  __shared__ double wsum[8];
+  for (int i = threadIdx.x; i < nr_vol; i += blockDim.x) srule[i] = rule_vol[i];
+  for (int i = threadIdx.x; i < nr_if; i += blockDim.x) srule[nr_vol + i] = rule_if[i];
+  if (threadIdx.x < 16) lut[threadIdx.x] = tab->e[DIM - 2][dt][threadIdx.x];
+  __syncthreads();
+  int64_t e = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  double sum = 0.0;
+  if (e < M.ne) {
+    int v[4], mask;
+    double ls[4], p[DIM + 1][DIM];
+    load_element<DIM>(M, lset, e, v, ls, p);
+    int dom = sign_test<DIM>(ls, mask);
+    if (dom == IF || dom == dt) {
+      ElGeom<DIM> G;
+      element_geometry<DIM>(p, G);
+      double meas = fabs(G.det);
+      if (dom != IF) {
+        for (int q = 0; q < nr_vol; q++) {
+          double4 r = srule[q];
+          double xi[3] = {r.x, r.y, r.z}, x[3];
+          map_point<DIM>(p, xi, x);
+          sum += meas * r.w * eval_poly(f, x);
+        }
+      } else {
+        const CutEntry E = lut[mask];
+        const double4 *rule = dt == IF ? srule + nr_vol : srule;
+        int nr = dt == IF ? nr_if : nr_vol;
+        double scale = dt == IF ? interface_scale<DIM>(G, ls) : 1.0;
+        for (int s = 0; s < E.ns; s++) {
+          double P[4][3];
+          for (int k = 0; k < E.npt; k++) coded_point<DIM>(E.v[s][k], ls, P[k]);
+          double fac = simplex_factor(E.npt, P) * scale;
+          for (int q = 0; q < nr; q++) {
+            double xi[3], x[3];
+            simplex_point(E.npt, P, rule[q], xi);
+            map_point<DIM>(p, xi, x);
+            sum += meas * (rule[q].w * fac) * eval_poly(f, x);
+          }
+        }
+      }
+    }
+  }
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) sum += __shfl_xor_sync(0xffffffffu, sum, o);
+  if ((threadIdx.x & 31) == 0) wsum[threadIdx.x >> 5] = sum;
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    double s = 0.0;
+    for (int w = 0; w < (int)(blockDim.x >> 5); w++) s += wsum[w];
+    partial[blockIdx.x] = s;
+  }
+}
+
+// second pass: one block, fixed association: thread t sums partial[t], partial[t+1024], ... then a fixed tree
+__global__ void __launch_bounds__(1024) k_reduce_final(int64_t n, const double *__restrict__ partial, double *__restrict__ out) {
+  __shared__ double s[1024];
+  double acc = 0.0;
+  for (int64_t i = threadIdx.x; i < n; i += 1024) acc += partial[i];
+  s[threadIdx.x] = acc;
+  __syncthreads();
+  for (int o = 512; o > 0; o >>= 1) {
+    if ((int)threadIdx.x < o) s[threadIdx.x] += s[threadIdx.x + o];
+    __syncthreads();
+  }
+  if (threadIdx.x == 0) out[0] = s[0];
+}
+
+__global__ void k_i32_to_i64(int64_t n, const int32_t *__restrict__ in, int64_t *__restrict__ out) {
+  int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n) out[i] = in[i];
+}
+
+// facet marking (xfem/cutinfo.cpp:191-255), one thread per facet, ballot -> word
+__global__ void __launch_bounds__(256) k_facets_neighbor_types(int64_t nf, const int32_t *__restrict__ f2e, const uint32_t *__restrict__ a,
+                                                              const uint32_t *__restrict__ b, int bva, int bvb, int use_and,
+                                                              uint32_t *__restrict__ out) {
+  int64_t f = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  bool r = false;
+  if (f < nf) {
+    int e0 = f2e[2 * f], e1 = f2e[2 * f + 1];
+    if (e0 >= 0) {
+      bool al = (a[e0 >> 5] >> (e0 & 31)) & 1, bl = (b[e0 >> 5] >> (e0 & 31)) & 1;
+      bool ar = e1 >= 0 ? ((a[e1 >> 5] >> (e1 & 31)) & 1) : (bva != 0);
+      bool br = e1 >= 0 ? ((b[e1 >> 5] >> (e1 & 31)) & 1) : (bvb != 0);
+      r = use_and ? ((al && br) || (ar && bl)) : (al || br || ar || bl);
+    }
+  }
+  unsigned w = __ballot_sync(0xffffffffu, r);
+  if ((threadIdx.x & 31) == 0 && (f >> 5) < ((nf + 31) >> 5)) out[f >> 5] = w;
+}
+
+__global__ void k_elements_with_neighbor_facets(int64_t nf, const int32_t *__restrict__ f2e, const uint32_t *__restrict__ fw,
+                                                uint32_t *__restrict__ out) {
+  int64_t f = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (f >= nf || !((fw[f >> 5] >> (f & 31)) & 1)) return;
+  for (int k = 0; k < 2; k++) {
+    int e = f2e[2 * f + k];
+    if (e >= 0) atomicOr(&out[e >> 5], 1u << (e & 31));
+  }
+}
+
+__global__ void k_dofs_of_elements(int64_t n, int nd, const int32_t *__restrict__ table, const uint32_t *__restrict__ a,
+                                   uint32_t *__restrict__ out) {
+  int64_t t = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (t >= n * nd) return;
+  int64_t e = t / nd;
+  if (!((a[e >> 5] >> (e & 31)) & 1)) return;
+  int d = table[t];
+  atomicOr(&out[d >> 5], 1u << (d & 31));
+}
+
+}  // namespace ngsx
+
+// =============================================================================================================
+// C ABI
+// =============================================================================================================
+using namespace ngsx;
+
+static inline unsigned nblocks(int64_t n, int bs) { return (unsigned)((n + bs - 1) / bs); }
+
+extern "C" {
+
+int ngsx_abi_version(void) { return NGSX_ABI_VERSION; }
+const char *ngsx_last_error(void) { return t_err.c_str(); }
+int64_t ngsx_launch_count(void) { return g_launches.load(); }
+
+int ngsx_interpolate_p1_clamp(int64_t nv, const double *in, double eps, double *out, void *stream) {
+  NGSX_REQUIRE(nv >= 0 && (nv == 0 || (in && out)), "interpolate_p1_clamp: bad arguments");
+  if (nv == 0) return NGSX_OK;
+  k_clamp<<<nblocks(nv, 256), 256, 0, as_stream(stream)>>>(nv, in, eps, out);
+  NGSX_LAUNCH_CHECK();
+  return NGSX_OK;
+}
+
+int ngsx_interpolate_p1_cf(const ngsx_mesh *mesh, int kind, const double *h_params, double eps, double *out, void *stream) {
+  if (int rc = check_mesh(mesh)) return rc;
+  NGSX_REQUIRE(kind >= 0 && kind <= NGSX_LSET_CYLZ && h_params && out, "interpolate_p1_cf: bad arguments");
+  if (mesh->nv == 0) return NGSX_OK;
+  LsetParams P;
+  memcpy(P.p, h_params, sizeof P.p);
+  k_lset_cf<<<nblocks(mesh->nv, 256), 256, 0, as_stream(stream)>>>(mesh->dim, mesh->nv, mesh->vert, kind, P, eps, out);
+  NGSX_LAUNCH_CHECK();
+  return NGSX_OK;
+}
+
+int ngsx_classify(const ngsx_mesh *mesh, const double *lset_v, uint32_t *cdom_words, int8_t *dom, double *ratio,
+                  int64_t *err, void *stream) {
+  if (int rc = check_mesh(mesh)) return rc;
+  NGSX_REQUIRE(lset_v || mesh->ne == 0, "classify: lset_v is NULL");
+  const DeviceData *dd = device_data();
+  if (!dd) return NGSX_ERR_CUDA;
+  cudaStream_t st = as_stream(stream);
+  if (err) {
+    int64_t init[2] = {0, INT64_MAX};
+    NGSX_CUDA(cudaMemcpyAsync(err, init, sizeof init, cudaMemcpyHostToDevice, st));
+  }
+  if (mesh->ne == 0) return NGSX_OK;
+  int64_t nwords = (mesh->ne + 31) / 32;
+  auto *e = reinterpret_cast<unsigned long long *>(err);
+  if (mesh->dim == 2) k_classify<2><<<nblocks(mesh->ne, 256), 256, 0, st>>>(*mesh, lset_v, dd->cut_table, cdom_words, nwords, dom, ratio, e);
+  else k_classify<3><<<nblocks(mesh->ne, 256), 256, 0, st>>>(*mesh, lset_v, dd->cut_table, cdom_words, nwords, dom, ratio, e);
+  NGSX_LAUNCH_CHECK();
+  return NGSX_OK;
+}
+
+int ngsx_node_marks(int64_t ne, int32_t npe, const int32_t *el2node, const int8_t *dom, const double *ratio,
+                    int64_t nnodes, int cell_mode, uint32_t *cut_nb_words, int32_t *dom_of_node, void *stream) {
+  NGSX_REQUIRE(ne >= 0 && dom && (cell_mode ? ratio != nullptr : (el2node != nullptr && npe > 0)), "node_marks: bad arguments");
+  (void)nnodes;
+  if (ne == 0) return NGSX_OK;
+  k_node_marks<<<nblocks(ne, 256), 256, 0, as_stream(stream)>>>(ne, npe, el2node, dom, ratio, cell_mode, cut_nb_words, dom_of_node);
+  NGSX_LAUNCH_CHECK();
+  return NGSX_OK;
+}
+
+static int lookup_rules(const DeviceData *dd, int dim, int order, const double4 **rv, int *nv, const double4 **ri, int *ni) {
+  if (!rule_lookup(dd, dim, order, rv, nv) || !rule_lookup(dd, dim - 1, order, ri, ni)) {
+    set_error("integration order beyond the tabulated reference rules");
+    return NGSX_ERR_UNSUPPORTED;
+  }
+  return NGSX_OK;
+}
+
+int ngsx_rule_count(const ngsx_mesh *mesh, const double *lset_v, int dt, int order, int32_t *npts, int64_t *err, void *stream) {
+  if (int rc = check_mesh(mesh)) return rc;
+  NGSX_REQUIRE(dt >= 0 && dt <= 2 && npts && lset_v, "rule_count: bad arguments");
+  const DeviceData *dd = device_data();
+  if (!dd) return NGSX_ERR_CUDA;
+  const double4 *rv, *ri;
+  int nv, ni;
+  if (int rc = lookup_rules(dd, mesh->dim, order, &rv, &nv, &ri, &ni)) return rc;
+  cudaStream_t st = as_stream(stream);
+  if (err) {
+    int64_t init[2] = {0, INT64_MAX};
+    NGSX_CUDA(cudaMemcpyAsync(err, init, sizeof init, cudaMemcpyHostToDevice, st));
+  }
+  if (mesh->ne == 0) return NGSX_OK;
+  auto *e = reinterpret_cast<unsigned long long *>(err);
+  if (mesh->dim == 2) k_rule_count<2><<<nblocks(mesh->ne, 256), 256, 0, st>>>(*mesh, lset_v, dd->cut_table, dt, nv, ni, npts, e);
+  else k_rule_count<3><<<nblocks(mesh->ne, 256), 256, 0, st>>>(*mesh, lset_v, dd->cut_table, dt, nv, ni, npts, e);
+  NGSX_LAUNCH_CHECK();
+  return NGSX_OK;
+}
+
+int ngsx_exclusive_scan(int64_t n, const int32_t *in, int64_t *out, void *stream) {
+  NGSX_REQUIRE(n >= 0 && out && (n == 0 || in), "exclusive_scan: bad arguments");
+  cudaStream_t st = as_stream(stream);
+  if (n == 0) { NGSX_CUDA(cudaMemsetAsync(out, 0, sizeof(int64_t), st)); return NGSX_OK; }
+  // widen into out[1..n], inclusive-scan in place, out[0] = 0
+  k_i32_to_i64<<<nblocks(n, 256), 256, 0, st>>>(n, in, out + 1);
+  NGSX_LAUNCH_CHECK();
+  NGSX_CUDA(cudaMemsetAsync(out, 0, sizeof(int64_t), st));
+  size_t tmp_bytes = 0;
+  NGSX_CUDA(cub::DeviceScan::InclusiveSum(nullptr, tmp_bytes, out + 1, out + 1, n, st));
+  void *tmp = nullptr;
+  NGSX_CUDA(cudaMallocAsync(&tmp, tmp_bytes, st));
+  cudaError_t e = cub::DeviceScan::InclusiveSum(tmp, tmp_bytes, out + 1, out + 1, n, st);
+  g_launches.fetch_add(2);
+  cudaFreeAsync(tmp, st);
+  NGSX_CUDA(e);
+  return NGSX_OK;
+}
+
+int ngsx_rule_fill(const ngsx_mesh *mesh, const double *lset_v, int dt, int order, int transform_if, int emit_uncut,
+                   const int64_t *offs, double *pts3, double *wts, void *stream) {
+  if (int rc = check_mesh(mesh)) return rc;
+  NGSX_REQUIRE(dt >= 0 && dt <= 2 && offs && pts3 && wts && lset_v, "rule_fill: bad arguments");
+  const DeviceData *dd = device_data();
+  if (!dd) return NGSX_ERR_CUDA;
+  const double4 *rv, *ri;
+  int nv, ni;
+  if (int rc = lookup_rules(dd, mesh->dim, order, &rv, &nv, &ri, &ni)) return rc;
+  if (mesh->ne == 0) return NGSX_OK;
+  cudaStream_t st = as_stream(stream);
+  unsigned nb = nblocks(mesh->ne * 32, 256);
+  if (mesh->dim == 2) k_rule_fill<2><<<nb, 256, 0, st>>>(*mesh, lset_v, dd->cut_table, dt, rv, nv, ri, ni, transform_if, emit_uncut, offs, pts3, wts);
+  else k_rule_fill<3><<<nb, 256, 0, st>>>(*mesh, lset_v, dd->cut_table, dt, rv, nv, ri, ni, transform_if, emit_uncut, offs, pts3, wts);
+  NGSX_LAUNCH_CHECK();
+  return NGSX_OK;
+}
+
+int ngsx_integrate(const ngsx_mesh *mesh, const double *lset_v, int dt, int order, const ngsx_poly *h_f, double *out, void *stream) {
+  if (int rc = check_mesh(mesh)) return rc;
+  NGSX_REQUIRE(dt >= 0 && dt <= 2 && h_f && out && lset_v, "integrate: bad arguments");
+  NGSX_REQUIRE(h_f->nterms >= 0 && h_f->nterms <= NGSX_POLY_MAXTERMS, "integrate: too many polynomial terms");
+  const DeviceData *dd = device_data();
+  if (!dd) return NGSX_ERR_CUDA;
+  const double4 *rv, *ri;
+  int nv, ni;
+  if (int rc = lookup_rules(dd, mesh->dim, order, &rv, &nv, &ri, &ni)) return rc;
+  cudaStream_t st = as_stream(stream);
+  if (mesh->ne == 0) { NGSX_CUDA(cudaMemsetAsync(out, 0, sizeof(double), st)); return NGSX_OK; }
+  PolyDev f;
+  f.n = h_f->nterms;
+  for (int m = 0; m < f.n; m++) { f.c[m] = h_f->coef[m]; for (int d = 0; d < 3; d++) f.ex[m][d] = h_f->ex[m][d]; }
+  unsigned nb = nblocks(mesh->ne, 256);
+  double *partial = nullptr;
+  NGSX_CUDA(cudaMallocAsync(&partial, nb * sizeof(double), st));
+  size_t smem = (size_t)(nv + ni) * sizeof(double4);
+  if (mesh->dim == 2) k_integrate<2><<<nb, 256, smem, st>>>(*mesh, lset_v, dd->cut_table, dt, rv, nv, ri, ni, f, partial);
+  else k_integrate<3><<<nb, 256, smem, st>>>(*mesh, lset_v, dd->cut_table, dt, rv, nv, ri, ni, f, partial);
+  g_launches.fetch_add(1);
+  cudaError_t e1 = cudaGetLastError();
+  k_reduce_final<<<1, 1024, 0, st>>>(nb, partial, out);
+  g_launches.fetch_add(1);
+  cudaError_t e2 = cudaGetLastError();
+  cudaFreeAsync(partial, st);
+  NGSX_CUDA(e1);
+  NGSX_CUDA(e2);
+  return NGSX_OK;
+}
+
+int ngsx_facets_neighbor_types(int64_t nf, const int32_t *facet2el, const uint32_t *a_words, const uint32_t *b_words,
+                               int bnd_val_a, int bnd_val_b, int use_and, uint32_t *out_words, void *stream) {
+  NGSX_REQUIRE(nf >= 0 && (nf == 0 || (facet2el && a_words && b_words && out_words)), "facets_neighbor_types: bad arguments");
+  if (nf == 0) return NGSX_OK;
+  k_facets_neighbor_types<<<nblocks(nf, 256), 256, 0, as_stream(stream)>>>(nf, facet2el, a_words, b_words, bnd_val_a, bnd_val_b, use_and, out_words);
+  NGSX_LAUNCH_CHECK();
+  return NGSX_OK;
+}
+
+int ngsx_elements_with_neighbor_facets(int64_t nf, const int32_t *facet2el, const uint32_t *facet_words,
+                                       int64_t ne, uint32_t *out_words, void *stream) {
+  NGSX_REQUIRE(nf >= 0 && ne >= 0 && (nf == 0 || (facet2el && facet_words)) && (ne == 0 || out_words), "elements_with_neighbor_facets: bad arguments");
+  cudaStream_t st = as_stream(stream);
+  if (ne > 0) NGSX_CUDA(cudaMemsetAsync(out_words, 0, ((ne + 31) / 32) * sizeof(uint32_t), st));
+  if (nf == 0) return NGSX_OK;
+  k_elements_with_neighbor_facets<<<nblocks(nf, 256), 256, 0, st>>>(nf, facet2el, facet_words, out_words);
+  NGSX_LAUNCH_CHECK();
+  return NGSX_OK;
+}
+
+int ngsx_dofs_of_elements(int64_t n, int32_t nd, const int32_t *table, const uint32_t *a_words, int64_t ndof, uint32_t *out_words, void *stream) {
+  NGSX_REQUIRE(n >= 0 && nd > 0 && ndof >= 0 && (n == 0 || (table && a_words)) && (ndof == 0 || out_words), "dofs_of_elements: bad arguments");
+  cudaStream_t st = as_stream(stream);
+  if (ndof > 0) NGSX_CUDA(cudaMemsetAsync(out_words, 0, ((ndof + 31) / 32) * sizeof(uint32_t), st));
+  if (n == 0) return NGSX_OK;
+  k_dofs_of_elements<<<nblocks(n * nd, 256), 256, 0, st>>>(n, nd, table, a_words, out_words);
+  NGSX_LAUNCH_CHECK();
+  return NGSX_OK;
+}
+
+}  // extern "C"

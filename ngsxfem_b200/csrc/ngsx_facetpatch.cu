@@ -1,0 +1,144 @@
+// ngsx_facetpatch.cu -- ghost-penalty facet-patch matrices (c-5):
+//   coef * h^hpow * (u - u.Other()) (v - v.Other())  integrated over BOTH elements of a facet patch
+// (SymbolicFacetPatchBilinearFormIntegrator::CalcFacetMatrix, xfem/symboliccutbfi.cpp:1202-1411; the tutorial form
+// py_tutorials/fictdom_ghostpen.py:105-107).  Volume rule of order 2*fe_order on each element (:1219-1220); every point
+// is evaluated in both elements -- the Newton pull-back of MapPatchIntegrationPoint (:1115-1199) is one exact
+// affine solve here.  One warp per patch: lane q stages the "jump vector" of point q in shared memory, then the
+// (2 nd)^2 entries are distributed over the lanes.
+#include "ngsx_host.cuh"
+
+namespace ngsx {
+
+constexpr int FP_WARPS = 4;
+
+template <int DIM>
+__device__ __forceinline__ void load_el_geo(const ngsx_mesh &M, int64_t e, double (*p)[DIM]) {
+  for (int k = 0; k <= DIM; k++) {
+    int v = __ldg(M.el2v + e * (DIM + 1) + k);
+#pragma unroll
+    for (int d = 0; d < DIM; d++) p[k][d] = __ldg(M.vert + (int64_t)v * DIM + d);
+  }
+}
+
+template <int DIM, int ORDER>
+__global__ void __launch_bounds__(FP_WARPS * 32) k_facetpatch(ngsx_mesh M, const double4 *__restrict__ rule, int nr, double coef, int hpow,
+                                                             int64_t npatch, const int32_t *__restrict__ patch_els, double *__restrict__ elmats) {
+  constexpr int ND = H1<DIM, ORDER>::ND, N2 = 2 * ND, NE = N2 * N2, T = (NE + 31) / 32;
+  extern __shared__ __align__(16) unsigned char smem_raw[];
+  double4 *srule = reinterpret_cast<double4 *>(smem_raw);
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  double *stage = reinterpret_cast<double *>(smem_raw + (size_t)nr * 32) + warp * (32 * N2 + 32);
+  double *facq = stage + 32 * N2;
+  for (int i = threadIdx.x; i < nr; i += blockDim.x) srule[i] = rule[i];
+  __syncthreads();
+  const int64_t nwarps = (int64_t)gridDim.x * FP_WARPS;
+  for (int64_t k = (int64_t)blockIdx.x * FP_WARPS + warp; k < npatch; k += nwarps) {
+    double p[2][DIM + 1][DIM];
+    ElGeom<DIM> G[2];
+    double hfac[2];
+    for (int s = 0; s < 2; s++) {
+      load_el_geo<DIM>(M, patch_els[2 * k + s], p[s]);
+      element_geometry<DIM>(p[s], G[s]);
+    }
+    {
+      // the coefficient is evaluated on mir1 for ALL patch points (symboliccutbfi.cpp:1359): h = mesh_size of element 0;
+      // the weight is the measure of the element the point lives on (mir1.GetWeight() after MapPatchIntegrationPoint)
+      double m0 = fabs(G[0].det);
+      double h = DIM == 2 ? sqrt(m0) : cbrt(m0);
+      double c = coef * ipow(h, hpow);
+      hfac[0] = c * m0;
+      hfac[1] = c * fabs(G[1].det);
+    }
+    double acc[T];
+#pragma unroll
+    for (int t = 0; t < T; t++) acc[t] = 0.0;
+    const int ntot = 2 * nr;
+    for (int q0 = 0; q0 < ntot; q0 += 32) {
+      const int nq = min(32, ntot - q0);
+      if (lane < nq) {
+        const int q = q0 + lane, side = q >= nr ? 1 : 0;
+        const double4 r = srule[q - side * nr];
+        double lam[4] = {r.x, r.y, r.z, 0.0}, last = 1.0;
+#pragma unroll
+        for (int kk = 0; kk < DIM; kk++) last -= lam[kk];
+        lam[DIM] = last;
+        double x[DIM];
+#pragma unroll
+        for (int d = 0; d < DIM; d++) {
+          double v = 0.0;
+#pragma unroll
+          for (int kk = 0; kk <= DIM; kk++) v += lam[kk] * p[side][kk][d];
+          x[d] = v;
+        }
+        // barycentrics of x in the other element: xi = Jinv_o (x - p_o[DIM])
+        double lo[4] = {0.0, 0.0, 0.0, 0.0}, lasto = 1.0;
+#pragma unroll
+        for (int kk = 0; kk < DIM; kk++) {
+          double v = 0.0;
+#pragma unroll
+          for (int d = 0; d < DIM; d++) v += G[1 - side].Jinv[kk][d] * (x[d] - p[1 - side][DIM][d]);
+          lo[kk] = v; lasto -= v;
+        }
+        lo[DIM] = lasto;
+        for (int i = 0; i < ND; i++) {
+          stage[lane * N2 + side * ND + i] = h1_shape<DIM, ORDER>(i, lam);
+          stage[lane * N2 + (1 - side) * ND + i] = -h1_shape<DIM, ORDER>(i, lo);
+        }
+        facq[lane] = hfac[side] * r.w;
+      }
+      __syncwarp();
+      for (int q = 0; q < nq; q++) {
+        const double f = facq[q];
+#pragma unroll
+        for (int t = 0; t < T; t++) {
+          int idx = lane + 32 * t;
+          if (idx < NE) acc[t] += f * stage[q * N2 + idx / N2] * stage[q * N2 + idx % N2];
+        }
+      }
+      __syncwarp();
+    }
+#pragma unroll
+    for (int t = 0; t < T; t++) {
+      int idx = lane + 32 * t;
+      if (idx < NE) elmats[k * NE + idx] = acc[t];
+    }
+  }
+}
+
+template <int DIM, int ORDER>
+static int launch_fp(const ngsx_mesh &M, const DeviceData *dd, const double4 *rule, int nr, double coef, int hpow, int64_t np,
+                     const int32_t *patch_els, double *elmats, cudaStream_t st) {
+  constexpr int N2 = 2 * H1<DIM, ORDER>::ND;
+  size_t smem = (size_t)nr * 32 + (size_t)FP_WARPS * (32 * N2 + 32) * 8;
+  auto kern = k_facetpatch<DIM, ORDER>;
+  NGSX_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  int64_t need = (np + FP_WARPS - 1) / FP_WARPS;
+  unsigned grid = (unsigned)std::max<int64_t>(1, std::min<int64_t>(need, (int64_t)dd->sm_count * 8));
+  kern<<<grid, FP_WARPS * 32, smem, st>>>(M, rule, nr, coef, hpow, np, patch_els, elmats);
+  NGSX_LAUNCH_CHECK();
+  return NGSX_OK;
+}
+
+}  // namespace ngsx
+
+using namespace ngsx;
+
+extern "C" int ngsx_facetpatch_elmat_h1(const ngsx_mesh *mesh, int fe_order, double coef, int hpow, int64_t npatch,
+                                        const int32_t *patch_els, double *elmats, void *stream) {
+  NGSX_REQUIRE(mesh && (mesh->dim == 2 || mesh->dim == 3) && mesh->vert && mesh->el2v, "facetpatch: bad mesh");
+  NGSX_REQUIRE(npatch >= 0 && (npatch == 0 || (patch_els && elmats)), "facetpatch: bad arguments");
+  if (fe_order < 1 || fe_order > 2) { set_error("facetpatch: H1 order outside the CUDA path (1, 2)"); return NGSX_ERR_UNSUPPORTED; }
+  const DeviceData *dd = device_data();
+  if (!dd) return NGSX_ERR_CUDA;
+  const double4 *rule; int nr;
+  if (!rule_lookup(dd, mesh->dim, 2 * fe_order, &rule, &nr)) { set_error("facetpatch: rule not tabulated"); return NGSX_ERR_UNSUPPORTED; }
+  if (npatch == 0) return NGSX_OK;
+  cudaStream_t st = as_stream(stream);
+  switch (mesh->dim * 10 + fe_order) {
+    case 21: return launch_fp<2, 1>(*mesh, dd, rule, nr, coef, hpow, npatch, patch_els, elmats, st);
+    case 22: return launch_fp<2, 2>(*mesh, dd, rule, nr, coef, hpow, npatch, patch_els, elmats, st);
+    case 31: return launch_fp<3, 1>(*mesh, dd, rule, nr, coef, hpow, npatch, patch_els, elmats, st);
+    case 32: return launch_fp<3, 2>(*mesh, dd, rule, nr, coef, hpow, npatch, patch_els, elmats, st);
+  }
+  return NGSX_ERR_UNSUPPORTED;
+}

@@ -1,0 +1,570 @@
+"""Host-side mirror of the reference's Python surface for the hot path (same names, argument meaning and error
+behaviour): python/__init__.py:107-378, xfem/python_xfem.cpp:50-815, utils/python_utils.cpp:21-153,
+cutint/python_cutint.cpp:20-81.  Every numerical step is one batched call into the C ABI (include/ngsx_abi.h);
+this file only validates arguments, owns device buffers (torch tensors) and caches the symbolic phase
+(sparsity graph, colouring, slot map).  Anything the CUDA path does not cover raises -- there is no CPU fallback."""
+import ctypes
+from typing import Dict, List, Optional
+
+import torch
+
+from . import _lib
+from ._lib import NEG, POS, IF, NgsxError, check
+from .ngs import (BND, VOL, AnalyticLevelset, BitArray, CSRMatrix, Expr, GridFunction, H1, Mesh, Poly, _ptr, _stream,
+                  require_cuda)
+
+# enums exported by python/python_ngsxfem.cpp:14-37
+NO, CDOM_NEG, CDOM_POS, UNCUT, CDOM_IF, HASNEG, HASPOS, ANY = range(8)
+FIRST, OPTIMAL, FALLBACK = 0, 1, 2      # QUAD_DIRECTION_POLICY (quads/hexes only; ignored on simplices)
+_DT2CDT = {NEG: CDOM_NEG, POS: CDOM_POS, IF: CDOM_IF}
+
+
+def _lib_():
+    return _lib.load()
+
+
+def _lset_vec(levelset) -> torch.Tensor:
+    """CF2GFForStraightCutRule (cutint/xintegration.cpp:91-103): only a GridFunction of order <= 1 on an H1 space takes the
+    straight-cut path.  The legacy subdivision path for general CoefficientFunctions is out of scope -> error."""
+    if isinstance(levelset, GridFunction) and levelset.space.order == 1:
+        return levelset.vec
+    raise NgsxError(-2, "level set must be a P1 GridFunction (InterpolateToP1 first); the legacy subdivlvl path of "
+                        "cutint/xintegration.cpp:696-1007 is outside the CUDA path")
+
+
+# ------------------------------------------------------------------------------------------------------------------
+def InterpolateToP1(coef, gf_p1: GridFunction, eps_perturbation: float = 1e-14, heapsize: int = 1000000):
+    """utils/python_utils.cpp:21-81 -> InterpolateP1::Do (utils/p1interpol.cpp:25-96)."""
+    mesh = gf_p1.space.mesh
+    out = gf_p1.vec
+    require_cuda(out, "gf_p1")
+    L = _lib_()
+    if isinstance(coef, GridFunction):                               # GridFunction branch: copy vertex dofs, clamp
+        src = coef.vec[: mesh.nv].contiguous()
+        check(L.ngsx_interpolate_p1_clamp(mesh.nv, _ptr(src), eps_perturbation, _ptr(out), _stream()))
+    elif isinstance(coef, AnalyticLevelset):
+        par = (ctypes.c_double * 8)(*coef.params)
+        check(L.ngsx_interpolate_p1_cf(ctypes.byref(mesh.c_struct()), coef.kind, par, eps_perturbation, _ptr(out), _stream()))
+    elif isinstance(coef, Poly) and coef.is_affine():
+        t = coef.terms
+        par = (ctypes.c_double * 8)(t.get((0, 0, 0), 0.0), t.get((1, 0, 0), 0.0), t.get((0, 1, 0), 0.0), t.get((0, 0, 1), 0.0), 0, 0, 0, 0)
+        check(L.ngsx_interpolate_p1_cf(ctypes.byref(mesh.c_struct()), _lib.LSET_AFFINE, par, eps_perturbation, _ptr(out), _stream()))
+    elif callable(coef):                                             # arbitrary CF: evaluated at the vertices by the host (plumbing)
+        cols = [mesh.vert[:, d] for d in range(mesh.dim)]
+        vals = coef(*cols).to(torch.float64).contiguous()
+        check(L.ngsx_interpolate_p1_clamp(mesh.nv, _ptr(vals), eps_perturbation, _ptr(out), _stream()))
+    else:
+        raise NgsxError(-2, "InterpolateToP1: unsupported coefficient")
+
+
+# ------------------------------------------------------------------------------------------------------------------
+class CutInfo:
+    """xfem/python_xfem.cpp:50-165 / CutInformation (xfem/cutinfo.cpp:11-188)."""
+
+    def __init__(self, mesh: Mesh, levelset=None, time_order: int = -1, heapsize: int = 1000000):
+        self.mesh = mesh
+        dev = mesh.device
+        self.nwords = (mesh.ne + 31) // 32
+        self.words = torch.zeros((8, self.nwords), dtype=torch.int32, device=dev)
+        self.dom = torch.zeros(mesh.ne, dtype=torch.int8, device=dev)
+        self.ratio = torch.zeros(mesh.ne, dtype=torch.float64, device=dev)
+        self.err = torch.zeros(2, dtype=torch.int64, device=dev)
+        self.cut_neighboring_node: Dict[str, BitArray] = {}
+        self.dom_of_node: Dict[str, torch.Tensor] = {}
+        if levelset is not None:
+            self.Update(levelset, time_order, heapsize)
+
+    def Mesh(self):
+        return self.mesh
+
+    def Update(self, levelset, time_order: int = -1, heapsize: int = 1000000, node_marks: bool = False):
+        if time_order >= 0:
+            raise NgsxError(-2, "space-time CutInfo (time_order >= 0) is outside the CUDA path")
+        lv = _lset_vec(levelset)
+        L = _lib_()
+        check(L.ngsx_classify(ctypes.byref(self.mesh.c_struct()), _ptr(lv), _ptr(self.words), _ptr(self.dom), _ptr(self.ratio),
+                              _ptr(self.err), _stream()))
+        if node_marks:
+            self._node_marks()
+        return self
+
+    def check_degenerate(self):
+        """the reference throws from inside Update on these level sets; here the kernel counts them"""
+        n, first = self.err.tolist()
+        if n:
+            raise NgsxError(-4, f"{n} element(s) carry a level set the reference rejects (first: element {first}): "
+                                "'You tried to cut a simplex with a plain geometry lset function'")
+
+    def _node_marks(self):
+        L = _lib_()
+        m = self.mesh
+        tables = {"vertex": (m.el2v, m.nv)}
+        e2v, el2e = m.edges()
+        tables["edge"] = (el2e.to(torch.int32).contiguous(), e2v.shape[0])
+        if m.dim == 3:
+            f2v, el2f = m.faces()
+            tables["face"] = (el2f.to(torch.int32).contiguous(), f2v.shape[0])
+        for name, (tab, nn) in tables.items():
+            ba = BitArray(nn, device=m.device)
+            don = torch.full((nn,), IF, dtype=torch.int32, device=m.device)
+            check(L.ngsx_node_marks(m.ne, tab.shape[1], _ptr(tab), _ptr(self.dom), _ptr(self.ratio), nn, 0, _ptr(ba.words), _ptr(don), _stream()))
+            self.cut_neighboring_node[name], self.dom_of_node[name] = ba, don
+        ba = BitArray(m.ne, device=m.device)
+        don = torch.full((m.ne,), IF, dtype=torch.int32, device=m.device)
+        check(L.ngsx_node_marks(m.ne, 0, None, _ptr(self.dom), _ptr(self.ratio), m.ne, 1, _ptr(ba.words), _ptr(don), _stream()))
+        self.cut_neighboring_node["element"], self.dom_of_node["element"] = ba, don
+
+    def GetElementsOfType(self, domain_type=IF, VOL_or_BND=VOL) -> BitArray:
+        """domain_type: DOMAIN_TYPE (NEG/POS/IF) or COMBINED_DOMAIN_TYPE (HASNEG, ...; the module constants are wrapped ints so
+        the two reference enums, which share small integers, stay distinguishable) -- xfem/python_xfem.cpp:91-118."""
+        if VOL_or_BND != VOL:
+            raise NgsxError(-2, "boundary-element CutInfo is outside the CUDA path")
+        cdt = domain_type.cdt if isinstance(domain_type, _CDT) else _DT2CDT[int(domain_type)]
+        return BitArray(self.mesh.ne, self.words[cdt])
+
+    def GetFacetsOfType(self, domain_type=IF) -> BitArray:
+        # Appendix C.1: facets_of_domain_type is never updated by the reference: NEG all ones, POS/IF all zeros
+        nf = self.mesh.nfacet
+        ba = BitArray(nf, device=self.mesh.device)
+        return ba.Set() if int(domain_type) == NEG and not isinstance(domain_type, _CDT) else ba
+
+    def GetCutRatios(self, VOL_or_BND=VOL) -> torch.Tensor:
+        return self.ratio
+
+
+class _CDT(int):
+    """COMBINED_DOMAIN_TYPE value"""
+    def __new__(cls, v):
+        o = int.__new__(cls, v)
+        o.cdt = v
+        return o
+
+
+NO, CDOM_NEG, CDOM_POS, UNCUT, CDOM_IF, HASNEG, HASPOS, ANY = (_CDT(i) for i in range(8))
+
+
+# ------------------------------------------------------------------------------------------------------------------
+def GetFacetsWithNeighborTypes(mesh: Mesh, a: BitArray, bnd_val_a: bool = True, bnd_val_b: bool = True, use_and: bool = True,
+                               b: Optional[BitArray] = None, heapsize: int = 1000000) -> BitArray:
+    """xfem/python_xfem.cpp:168-214 / xfem/cutinfo.cpp:191-255"""
+    if b is None:
+        b = a
+    _, f2e = mesh.facets()
+    out = BitArray(f2e.shape[0], device=mesh.device)
+    check(_lib_().ngsx_facets_neighbor_types(f2e.shape[0], _ptr(f2e), _ptr(a.words), _ptr(b.words), int(bnd_val_a), int(bnd_val_b),
+                                             int(use_and), _ptr(out.words), _stream()))
+    return out
+
+
+def GetElementsWithNeighborFacets(mesh: Mesh, a: BitArray, heapsize: int = 1000000) -> BitArray:
+    """xfem/cutinfo.cpp:257-279"""
+    _, f2e = mesh.facets()
+    out = BitArray(mesh.ne, device=mesh.device)
+    check(_lib_().ngsx_elements_with_neighbor_facets(f2e.shape[0], _ptr(f2e), _ptr(a.words), mesh.ne, _ptr(out.words), _stream()))
+    return out
+
+
+def GetDofsOfElements(space: H1, a: BitArray, heapsize: int = 1000000) -> BitArray:
+    """xfem/cutinfo.cpp:281-304"""
+    out = BitArray(space.ndof, device=space.mesh.device)
+    check(_lib_().ngsx_dofs_of_elements(space.mesh.ne, space.nd, _ptr(space.el2dof), _ptr(a.words), space.ndof, _ptr(out.words), _stream()))
+    return out
+
+
+# ------------------------------------------------------------------------------------------------------------------
+def _poly_of(cf):
+    if cf is None:
+        return _lib.make_poly(None)
+    p = Poly.lift(cf)
+    if p is None:
+        raise NgsxError(-2, "only polynomial coefficient functions are on the CUDA path")
+    return _lib.make_poly(p.as_terms())
+
+
+def IntegrateX(lset, mesh: Mesh, cf=None, order: int = 5, domain_type=IF, subdivlvl: int = 0, time_order: int = -1,
+               quad_dir_policy=OPTIMAL, heapsize: int = 1000000, sync: bool = True):
+    """cutint/python_cutint.cpp:20-72.  Deterministic tree reduction on the device (the reference's AtomicAdd order is not)."""
+    if subdivlvl != 0 or time_order >= 0:
+        raise NgsxError(-2, "subdivlvl > 0 / space-time integration is outside the CUDA path")
+    lv = _lset_vec(lset)
+    out = torch.zeros(1, dtype=torch.float64, device=mesh.device)
+    poly = _poly_of(cf)
+    check(_lib_().ngsx_integrate(ctypes.byref(mesh.c_struct()), _ptr(lv), int(domain_type), order, ctypes.byref(poly), _ptr(out), _stream()))
+    return float(out.item()) if sync else out
+
+
+def Integrate(levelset_domain=None, cf=None, mesh=None, order=5, time_order=-1, heapsize=1000000, **kwargs):
+    """python/__init__.py:311-378: Integrate(levelset_domain={...}, cf=..., mesh=..., order=...)"""
+    if levelset_domain is None or not isinstance(levelset_domain, dict):
+        raise NgsxError(-2, "only Integrate(levelset_domain=...) is provided (plain NGSolve Integrate is not part of the path)")
+    if mesh is None:
+        raise NgsxError(-1, "Integrate needs cf and mesh")
+    ld = dict(levelset_domain)
+    if "levelset" not in ld or "domain_type" not in ld:
+        raise NgsxError(-1, "levelset_domain needs 'levelset' and 'domain_type'")            # python/__init__.py:281-307
+    return IntegrateX(lset=ld["levelset"], mesh=mesh, cf=cf, order=order, domain_type=ld["domain_type"],
+                      subdivlvl=ld.get("subdivlvl", 0), time_order=time_order,
+                      quad_dir_policy=ld.get("quad_dir_policy", OPTIMAL), heapsize=heapsize)
+
+
+# ------------------------------------------------------------------------------------------------------------------
+# integrators
+# ------------------------------------------------------------------------------------------------------------------
+def _single(d: Dict[int, float], what):
+    if len(d) != 1:
+        raise NgsxError(-2, f"{what}: one power of h per term is supported")
+    (p, c), = d.items()
+    return c, p
+
+
+class SymbolicCutBFI:
+    """xfem/python_xfem.cpp:450-532 -> SymbolicCutBilinearFormIntegrator (xfem/symboliccutbfi.cpp:19-315)"""
+
+    def __init__(self, lset, domain_type=NEG, force_intorder: int = -1, time_order: int = -1, subdivlvl: int = 0,
+                 quad_dir_policy=OPTIMAL, form: Expr = None, VOL_or_BND=VOL, element_boundary: bool = False, skeleton: bool = False,
+                 definedon=None, definedonelements: Optional[BitArray] = None, deformation=None):
+        if form is None:
+            raise NgsxError(-1, "form is required")
+        if VOL_or_BND != VOL or element_boundary or skeleton:
+            raise NgsxError(-2, "element_boundary / skeleton / BND cut integrators are outside the CUDA path")
+        if time_order >= 0 or subdivlvl != 0 or deformation is not None or definedon is not None:
+            raise NgsxError(-2, "time_order / subdivlvl / deformation / definedon are outside the CUDA path")
+        self.lset, self.dt, self.force_intorder, self.definedonelements = lset, int(domain_type), force_intorder, definedonelements
+        terms = form.collect()
+        f = _lib.FormH1()
+        difforder_trial, difforder_test = 99, 99
+        nit = {}
+        for atoms, d in terms.items():
+            c, p = _single(d, "SymbolicCutBFI")
+            if atoms == ("gugv",):
+                f.c_stiff, f.hpow_stiff = c, p
+                difforder_trial, difforder_test = min(difforder_trial, 1), min(difforder_test, 1)
+            elif atoms == ("u", "v"):
+                f.c_mass, f.hpow_mass = c, p
+                difforder_trial, difforder_test = 0, 0
+            elif atoms in (("gun", "v"), ("gvn", "u")):
+                nit[atoms] = (c, p)
+            else:
+                raise NgsxError(-2, f"form term {atoms} is outside the CUDA path (supported: grad(u)*grad(v), u*v, "
+                                    "(grad(u)*n)*v + (grad(v)*n)*u with n = LevelsetNormal()); no CPU fallback")
+        if nit:
+            if len(nit) != 2 or nit[("gun", "v")] != nit[("gvn", "u")]:
+                raise NgsxError(-2, "the Nitsche consistency terms must appear as the symmetric pair")
+            f.c_nitsche, f.hpow_nitsche = nit[("gun", "v")]
+            difforder_trial, difforder_test = 0, 0           # proxies u (0) and grad u (1) both present: min = 0
+        self.form = f
+        self.difforders = (difforder_trial, difforder_test)
+
+    def intorder(self, fe_order: int) -> int:
+        """xfem/symboliccutbfi.cpp:97-113"""
+        if self.force_intorder >= 0:
+            return self.force_intorder
+        return 2 * fe_order - (self.difforders[0] + self.difforders[1])
+
+
+class SymbolicCutLFI:
+    """xfem/python_xfem.cpp:608-670 -> SymbolicCutLinearFormIntegrator (xfem/symboliccutlfi.cpp:52-158)"""
+
+    def __init__(self, lset, domain_type=NEG, force_intorder: int = -1, time_order: int = -1, subdivlvl: int = 0,
+                 quad_dir_policy=OPTIMAL, form=None, VOL_or_BND=VOL, element_boundary: bool = False, skeleton: bool = False,
+                 definedon=None, definedonelements: Optional[BitArray] = None, deformation=None):
+        if VOL_or_BND != VOL or element_boundary or skeleton or time_order >= 0 or subdivlvl != 0 or deformation is not None:
+            raise NgsxError(-2, "this SymbolicCutLFI variant is outside the CUDA path")
+        self.lset, self.dt, self.force_intorder, self.definedonelements = lset, int(domain_type), force_intorder, definedonelements
+        # form = f * v with f a polynomial CoefficientFunction (py_tutorials/fictdom_ghostpen.py:98: coeff_f*v)
+        if not isinstance(form, Expr) or len(form.terms) != 1 or form.terms[0][1] != 0 or form.terms[0][2] != ("v",):
+            raise NgsxError(-2, "SymbolicCutLFI: form must be f*v with a polynomial f; no CPU fallback")
+        self.coef = (form.poly if form.poly is not None else Poly({(0, 0, 0): 1.0})) * form.terms[0][0]
+
+    def intorder(self, fe_order):
+        return self.force_intorder if self.force_intorder >= 0 else 2 * fe_order       # xfem/symboliccutlfi.cpp:85
+
+
+class SymbolicFacetPatchBFI:
+    """xfem/python_xfem.cpp:534-606 -> SymbolicFacetPatchBilinearFormIntegrator (xfem/symboliccutbfi.cpp:1202-1411)"""
+
+    def __init__(self, form: Expr = None, force_intorder: int = -1, time_order: int = -1, skeleton: bool = True,
+                 definedonelements: Optional[BitArray] = None, deformation=None):
+        if skeleton:
+            raise NgsxError(-2, "skeleton=True (derivative-jump ghost penalty, xfem/ghostpenalty.cpp) is outside the CUDA path; "
+                                "use skeleton=False (facet-patch)")
+        if time_order >= 0 or deformation is not None:
+            raise NgsxError(-2, "space-time / deformed facet patches are outside the CUDA path")
+        terms = form.collect()
+        want = {("u", "v"): 1.0, ("uo", "v"): -1.0, ("u", "vo"): -1.0, ("uo", "vo"): 1.0}
+        if set(terms) != set(want):
+            raise NgsxError(-2, "facet-patch form must be c*h^p*(u-u.Other())*(v-v.Other())")
+        c, p = _single(terms[("u", "v")], "SymbolicFacetPatchBFI")
+        for a, s in want.items():
+            if _single(terms[a], "SymbolicFacetPatchBFI") != (s * c, p):
+                raise NgsxError(-2, "facet-patch form must be c*h^p*(u-u.Other())*(v-v.Other())")
+        self.coef, self.hpow, self.definedonelements = c, p, definedonelements    # note: force_intorder is ignored by the reference too (Appendix C.2)
+
+
+def SymbolicBFI(levelset_domain=None, *args, **kwargs):
+    """python/__init__.py:107-192"""
+    if levelset_domain is None or not isinstance(levelset_domain, dict):
+        raise NgsxError(-2, "only SymbolicBFI(levelset_domain=...) is provided")
+    ld = dict(levelset_domain)
+    if "levelset" not in ld or "domain_type" not in ld:
+        raise NgsxError(-1, "levelset_domain needs 'levelset' and 'domain_type'")
+    form = kwargs.pop("form", args[0] if args else None)
+    return SymbolicCutBFI(lset=ld["levelset"], domain_type=ld["domain_type"], force_intorder=ld.get("force_intorder", -1),
+                          subdivlvl=ld.get("subdivlvl", 0), quad_dir_policy=ld.get("quad_dir_policy", OPTIMAL), form=form, **kwargs)
+
+
+def SymbolicLFI(levelset_domain=None, *args, **kwargs):
+    """python/__init__.py:194-279"""
+    if levelset_domain is None or not isinstance(levelset_domain, dict):
+        raise NgsxError(-2, "only SymbolicLFI(levelset_domain=...) is provided")
+    ld = dict(levelset_domain)
+    form = kwargs.pop("form", args[0] if args else None)
+    return SymbolicCutLFI(lset=ld["levelset"], domain_type=ld["domain_type"], force_intorder=ld.get("force_intorder", -1),
+                          subdivlvl=ld.get("subdivlvl", 0), quad_dir_policy=ld.get("quad_dir_policy", OPTIMAL), form=form, **kwargs)
+
+
+# ------------------------------------------------------------------------------------------------------------------
+# forms: symbolic phase (graph, colouring, slot map) cached; numeric phase = one fused launch sequence per integrator
+# ------------------------------------------------------------------------------------------------------------------
+class _Plan:
+    """colour-sorted element list + slot map of one integrator"""
+
+    def __init__(self, els, table, color_ptr, group, slots=None):
+        self.els, self.table, self.color_ptr, self.group, self.slots = els, table, color_ptr, group, slots
+        self.ncolors = len(color_ptr) - 1
+        self.h_color_ptr = (ctypes.c_int64 * len(color_ptr))(*color_ptr)
+
+
+def color_list(table: torch.Tensor, ndof: int, group: int):
+    """ngsx_color_groups on the host copy of a dof table [n][nd]; returns (perm (device), color_ptr list)"""
+    n, nd = table.shape
+    h_table = table.cpu().contiguous()
+    perm = torch.empty(n, dtype=torch.int64)
+    cap = 1024
+    cptr = torch.zeros(cap + 1, dtype=torch.int64)
+    nc = ctypes.c_int32(0)
+    check(_lib_().ngsx_color_groups(n, nd, h_table.data_ptr(), ndof, group, perm.data_ptr(), cptr.data_ptr(), cap, ctypes.byref(nc)))
+    return perm.to(table.device), cptr[: nc.value + 1].tolist()
+
+
+class BilinearForm:
+    """T_BilinearForm<double> stand-in: `a += integrator`, `a.Assemble()`, `a.mat` (CSR on the device).
+    The sparsity is the full element (and, with dgjumps, facet-patch) graph like NGSolve's GetGraph."""
+    group_size = 6
+
+    def __init__(self, space: H1, symmetric: bool = False, check_unused: bool = False, **_):
+        self.space = space
+        self.integrators: List = []
+        self.mat: Optional[CSRMatrix] = None
+        self._plans: Dict[int, _Plan] = {}
+        self._graph_key = None
+
+    def __iadd__(self, integ):
+        if not isinstance(integ, (SymbolicCutBFI, SymbolicFacetPatchBFI)):
+            raise NgsxError(-2, "only SymbolicCutBFI / SymbolicFacetPatchBFI integrators are on the CUDA path")
+        self.integrators.append(integ)
+        return self
+
+    # --- which elements / facets couple (overridden by RestrictedBilinearForm) ---
+    def _graph_elements(self) -> Optional[torch.Tensor]:
+        return None            # all
+
+    def _graph_facets(self) -> Optional[torch.Tensor]:
+        if not self.space.dgjumps:
+            return torch.zeros(0, dtype=torch.int64, device=self.space.mesh.device)
+        _, f2e = self.space.mesh.facets()
+        return torch.nonzero(f2e[:, 1] >= 0).reshape(-1)
+
+    def _build_graph(self):
+        """RestrictedBilinearForm::GetGraph (utils/restrictedblf.cpp:22-138) on the device"""
+        L = _lib_()
+        fes = self.space
+        g = ctypes.c_void_p()
+        check(L.ngsx_csr_graph_create(fes.ndof, ctypes.byref(g)))
+        try:
+            els = self._graph_elements()
+            tab = fes.el2dof if els is None else fes.el2dof[els].contiguous()
+            check(L.ngsx_csr_graph_add_table(g, tab.shape[0], fes.nd, _ptr(tab), _stream()))
+            fac = self._graph_facets()
+            if fac is not None and fac.numel() > 0:
+                _, f2e = fes.mesh.facets()
+                pe = f2e[fac].long()
+                ptab = torch.cat([fes.el2dof[pe[:, 0]], fes.el2dof[pe[:, 1]]], dim=1).contiguous()
+                check(L.ngsx_csr_graph_add_table(g, ptab.shape[0], 2 * fes.nd, _ptr(ptab), _stream()))
+            nnz = ctypes.c_int64(0)
+            check(L.ngsx_csr_graph_finalize(g, ctypes.byref(nnz), _stream()))
+            if nnz.value >= 2 ** 31:
+                raise NgsxError(-5, "more than 2^31 non-zeros: int32 slot map exhausted")
+            dev = fes.mesh.device
+            rowptr = torch.empty(fes.ndof + 1, dtype=torch.int64, device=dev)
+            colidx = torch.empty(nnz.value, dtype=torch.int32, device=dev)
+            check(L.ngsx_csr_graph_export(g, _ptr(rowptr), _ptr(colidx), _stream()))
+            torch.cuda.current_stream().synchronize()
+        finally:
+            L.ngsx_csr_graph_destroy(g)
+        self.mat = CSRMatrix(fes.ndof, rowptr, colidx, torch.zeros(nnz.value, dtype=torch.float64, device=dev))
+
+    def _active_elements(self, integ: SymbolicCutBFI) -> torch.Tensor:
+        """elements on which the reference's CalcElementMatrixAdd gets a non-null rule (+ definedonelements)"""
+        ci = CutInfo(self.space.mesh, integ.lset)
+        cdt = {NEG: HASNEG, POS: HASPOS, IF: CDOM_IF}[integ.dt]
+        ba = ci.GetElementsOfType(cdt)
+        if integ.definedonelements is not None:
+            ba = ba & integ.definedonelements
+        return ba.nonzero()
+
+    def _plan_for(self, k: int, integ) -> _Plan:
+        if k in self._plans:
+            return self._plans[k]
+        fes, L = self.space, _lib_()
+        if isinstance(integ, SymbolicCutBFI):
+            els = self._active_elements(integ)
+            table = fes.el2dof[els].contiguous()
+            perm, cptr = color_list(table, fes.ndof, self.group_size)
+            els_s = els[perm].to(torch.int32).contiguous()
+            table_s = table[perm].contiguous()
+            slots = torch.empty((els_s.numel(), fes.nd * fes.nd), dtype=torch.int32, device=fes.mesh.device)
+            check(L.ngsx_slot_map(els_s.numel(), fes.nd, _ptr(table_s), _ptr(self.mat.rowptr), _ptr(self.mat.colidx), _ptr(slots), _stream()))
+            if els_s.numel() and int(slots.min().item()) < 0:
+                raise NgsxError(-1, "an element coupling is missing from the sparsity pattern (element_restriction too small?)")
+            plan = _Plan(els_s, table_s, cptr, self.group_size, slots)
+        else:
+            plan = self._facetpatch_plan(integ)
+        self._plans[k] = plan
+        return plan
+
+    def _facetpatch_plan(self, integ: SymbolicFacetPatchBFI):
+        fes, L = self.space, _lib_()
+        mesh = fes.mesh
+        _, f2e = mesh.facets()
+        inner = f2e[:, 1] >= 0
+        if integ.definedonelements is not None:
+            inner = inner & integ.definedonelements.to_bool()
+        fac = torch.nonzero(inner).reshape(-1)
+        pe = f2e[fac].contiguous()                                     # [np][2] int32, element 0 = lower number
+        tab = torch.cat([fes.el2dof[pe[:, 0].long()], fes.el2dof[pe[:, 1].long()]], dim=1).contiguous()
+        # compressed dof list per patch (NGS/comp/bilinearform.cpp:1800-1853): duplicates -> first occurrence, rest -1
+        n2 = tab.shape[1]
+        eq = tab[:, :, None] == tab[:, None, :]
+        first = torch.argmax(eq.int(), dim=2)                          # first index holding the same dof
+        rep = first.to(torch.int32).contiguous()
+        perm, cptr = color_list(tab, fes.ndof, 1)
+        pe_s, tab_s, rep_s = pe[perm].contiguous(), tab[perm].contiguous(), rep[perm].contiguous()
+        slots = torch.empty((pe_s.shape[0], n2 * n2), dtype=torch.int32, device=mesh.device)
+        check(L.ngsx_slot_map(pe_s.shape[0], n2, _ptr(tab_s), _ptr(self.mat.rowptr), _ptr(self.mat.colidx), _ptr(slots), _stream()))
+        if pe_s.shape[0] and int(slots.min().item()) < 0:
+            raise NgsxError(-1, "facet-patch coupling missing from the sparsity pattern (dgjumps=True / facet_restriction needed)")
+        plan = _Plan(pe_s, tab_s, cptr, 1, slots)
+        plan.rep = rep_s
+        return plan
+
+    def Assemble(self, reallocate: bool = False):
+        """S_BilinearForm::DoAssemble (NGS/comp/bilinearform.cpp:929-1575): SetZero, then every integrator colour by colour"""
+        L = _lib_()
+        fes = self.space
+        if self.mat is None or reallocate:
+            self._build_graph()
+            self._plans.clear()
+        self.mat.vals.zero_()
+        mesh_c = ctypes.byref(fes.mesh.c_struct())
+        for k, integ in enumerate(self.integrators):
+            plan = self._plan_for(k, integ)
+            if isinstance(integ, SymbolicCutBFI):
+                lv = _lset_vec(integ.lset)
+                check(L.ngsx_assemble_csr_h1(mesh_c, _ptr(lv), fes.order, integ.dt, integ.intorder(fes.order), ctypes.byref(integ.form),
+                                             plan.els.numel(), _ptr(plan.els), _ptr(plan.slots), plan.ncolors, plan.h_color_ptr,
+                                             plan.group, _ptr(self.mat.vals), _stream()))
+            else:
+                self._assemble_facetpatch(integ, plan)
+        return self
+
+    def _assemble_facetpatch(self, integ, plan):
+        """patch matrices on the device (ngsx_facetpatch_elmat_h1), duplicate dofs merged like NGSolve's compressed_elmat,
+        then a deterministic index_add in patch order (host-orchestrated torch scatter: plumbing for the NEXT row f-1)."""
+        L = _lib_()
+        fes = self.space
+        npatch = plan.els.shape[0]
+        if npatch == 0:
+            return
+        n2 = 2 * fes.nd
+        em = torch.empty((npatch, n2 * n2), dtype=torch.float64, device=fes.mesh.device)
+        check(L.ngsx_facetpatch_elmat_h1(ctypes.byref(fes.mesh.c_struct()), fes.order, integ.coef, integ.hpow, npatch,
+                                         _ptr(plan.els), _ptr(em), _stream()))
+        # merge duplicate dofs of the two halves (NGSolve's compressed_elmat): C[rep[i], i] = 1, em_c = C em C^T
+        rep = plan.rep.long()
+        C = torch.zeros((npatch, n2, n2), dtype=torch.float64, device=em.device)
+        C.scatter_(1, rep[:, None, :], 1.0)
+        em_c = torch.bmm(torch.bmm(C, em.view(npatch, n2, n2)), C.transpose(1, 2))
+        is_rep = rep == torch.arange(n2, device=em.device)[None, :]
+        keep = (is_rep[:, :, None] & is_rep[:, None, :]).reshape(npatch, -1)
+        for c in range(plan.ncolors):            # colour by colour: slots are unique inside a colour -> plain deterministic +=
+            a, b = plan.color_ptr[c], plan.color_ptr[c + 1]
+            k = keep[a:b].reshape(-1)
+            idx = plan.slots[a:b].reshape(-1)[k].long()
+            self.mat.vals[idx] += em_c[a:b].reshape(-1)[k]
+
+    def elmats(self, k: int = 0):
+        """dense element matrices of integrator k for its active elements (the per-element view CalcElementMatrixAdd would serve)"""
+        integ, fes, L = self.integrators[k], self.space, _lib_()
+        els = self._active_elements(integ).to(torch.int32).contiguous()
+        out = torch.empty((els.numel(), fes.nd, fes.nd), dtype=torch.float64, device=fes.mesh.device)
+        npts = torch.empty(els.numel(), dtype=torch.int32, device=fes.mesh.device)
+        check(L.ngsx_elmat_h1(ctypes.byref(fes.mesh.c_struct()), _ptr(_lset_vec(integ.lset)), fes.order, integ.dt, integ.intorder(fes.order),
+                              ctypes.byref(integ.form), els.numel(), _ptr(els), _ptr(out), _ptr(npts), _stream()))
+        return els, out, npts
+
+
+class RestrictedBilinearForm(BilinearForm):
+    """utils/python_utils.cpp:86-153 / utils/restrictedblf.cpp: sparsity restricted to marked elements / facets"""
+
+    def __init__(self, space: H1, name: str = "bfa", element_restriction: Optional[BitArray] = None,
+                 facet_restriction: Optional[BitArray] = None, check_unused: bool = True, **flags):
+        super().__init__(space, **flags)
+        self.element_restriction, self.facet_restriction = element_restriction, facet_restriction
+
+    def _graph_elements(self):
+        return None if self.element_restriction is None else self.element_restriction.nonzero()
+
+    def _graph_facets(self):
+        if self.facet_restriction is None:
+            return super()._graph_facets()
+        _, f2e = self.space.mesh.facets()
+        return torch.nonzero(self.facet_restriction.to_bool() & (f2e[:, 1] >= 0)).reshape(-1)
+
+
+class LinearForm:
+    group_size = 6
+
+    def __init__(self, space: H1):
+        self.space = space
+        self.integrators: List[SymbolicCutLFI] = []
+        self.vec = torch.zeros(space.ndof, dtype=torch.float64, device=space.mesh.device)
+        self._plans: Dict[int, _Plan] = {}
+
+    def __iadd__(self, integ):
+        if not isinstance(integ, SymbolicCutLFI):
+            raise NgsxError(-2, "only SymbolicCutLFI integrators are on the CUDA path")
+        self.integrators.append(integ)
+        return self
+
+    def Assemble(self):
+        """NGS/comp/linearform.cpp:209-243"""
+        L = _lib_()
+        fes = self.space
+        self.vec.zero_()
+        for k, integ in enumerate(self.integrators):
+            if k not in self._plans:
+                ci = CutInfo(fes.mesh, integ.lset)
+                ba = ci.GetElementsOfType({NEG: HASNEG, POS: HASPOS, IF: CDOM_IF}[integ.dt])
+                if integ.definedonelements is not None:
+                    ba = ba & integ.definedonelements
+                els = ba.nonzero()
+                table = fes.el2dof[els].contiguous()
+                perm, cptr = color_list(table, fes.ndof, self.group_size)
+                self._plans[k] = _Plan(els[perm].to(torch.int32).contiguous(), table[perm].contiguous(), cptr, self.group_size)
+            plan = self._plans[k]
+            poly = _poly_of(integ.coef)
+            check(L.ngsx_assemble_vec_h1(ctypes.byref(fes.mesh.c_struct()), _ptr(_lset_vec(integ.lset)), fes.order, integ.dt,
+                                         integ.intorder(fes.order), ctypes.byref(poly), plan.els.numel(), _ptr(plan.els), _ptr(plan.table),
+                                         plan.ncolors, plan.h_color_ptr, plan.group, _ptr(self.vec), _stream()))
+        return self

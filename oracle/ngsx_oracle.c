@@ -632,12 +632,12 @@ void orc_dofs_of_elements(int64_t ne, int nd, int64_t ndof, const int32_t *el2do
 }
 
 /* xfem/symboliccutbfi.cpp:1202-1411 SymbolicFacetPatchBilinearFormIntegrator::CalcFacetMatrix for the ghost-penalty form
- *   c * (u - u.Other()) * (v - v.Other())       (py_tutorials/fictdom_ghostpen.py:105-107)
+ *   c * h^hpow * (u - u.Other()) * (v - v.Other())       (py_tutorials/fictdom_ghostpen.py:105-107)
  * on affine simplices: volume rules of order 2*fe_order on BOTH elements (:1219-1220); each point is pulled back into
  * the other element (MapPatchIntegrationPoint :1115-1199 -- exact in one step for affine maps); weight mir.GetWeight().
  * elmat is (2 nd)x(2 nd) row-major over [dofs of el1 | dofs of el2]. */
 int orc_facetpatch_elmat_h1(int dim, int fe_order, const int *vn1, const double *pmat1, const int *vn2, const double *pmat2,
-                            double coef, double *elmat)
+                            double coef, int hpow, double *elmat)
 {
   int nd = orc_h1_ndof(dim, fe_order), n2 = 2*nd;
   const double (*r)[4];
@@ -647,6 +647,9 @@ int orc_facetpatch_elmat_h1(int dim, int fe_order, const int *vn1, const double 
   affine_init(dim, pmat1, &A[0]);
   affine_init(dim, pmat2, &A[1]);
   for (int i = 0; i < n2*n2; i++) elmat[i] = 0;
+  /* the coefficient (h = specialcf.mesh_size, NGS/fem/python_fem.cpp:564-593) is evaluated on mir1, i.e. on element 1,
+   * for all patch points (:1359) */
+  coef *= pow(pow(fabs(A[0].det), 1.0 / dim), hpow);
   double sh[2][ORC_MAXND], dref[ORC_MAXND*3], jump[2*ORC_MAXND];
   for (int side = 0; side < 2; side++) {
     const affine_t *Ah = &A[side], *Ao = &A[1-side];

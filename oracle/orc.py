@@ -61,7 +61,7 @@ def load():
     L.orc_facets_neighbor_types.argtypes = [c_i64, ip, ubp, ubp, c_int, c_int, c_int, ubp]
     L.orc_elements_with_neighbor_facets.argtypes = [c_i64, c_i64, ip, ubp, ubp]
     L.orc_dofs_of_elements.argtypes = [c_i64, c_int, c_i64, ip, ubp, ubp]
-    L.orc_facetpatch_elmat_h1.argtypes = [c_int, c_int, ip, dp, ip, dp, c_double, dp]
+    L.orc_facetpatch_elmat_h1.argtypes = [c_int, c_int, ip, dp, ip, dp, c_double, c_int, dp]
     L.orc_set_threads.argtypes = [c_int]
     _LIB = L
     return L
@@ -163,11 +163,11 @@ def elvec_h1(dim, fe_order, vnums, pmat, lset, dt, intorder, mono, impl="oracle"
     return n, ev
 
 
-def facetpatch_elmat_h1(dim, fe_order, vn1, pmat1, vn2, pmat2, coef):
+def facetpatch_elmat_h1(dim, fe_order, vn1, pmat1, vn2, pmat2, coef, hpow=0):
     nd = load().orc_h1_ndof(dim, fe_order)
     em = np.zeros((2 * nd, 2 * nd))
     a, b, p1, p2 = _i(vn1), _i(vn2), _d(pmat1), _d(pmat2)
-    n = load().orc_facetpatch_elmat_h1(dim, fe_order, P(a, ip), P(p1), P(b, ip), P(p2), coef, P(em))
+    n = load().orc_facetpatch_elmat_h1(dim, fe_order, P(a, ip), P(p1), P(b, ip), P(p2), coef, hpow, P(em))
     return n, em
 
 

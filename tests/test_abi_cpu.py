@@ -1,0 +1,119 @@
+"""CPU-side checks of the product library: it loads, exports every symbol include/ngsx_abi.h declares, its host-only
+entry points work (greedy group colouring), argument errors come back as statuses, and the host-side mirror of the
+reference's Python surface parses the tutorial forms.  No kernel is launched here."""
+import ctypes
+import os
+import re
+
+import numpy as np
+import pytest
+import torch
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+@pytest.fixture(scope="module")
+def lib():
+    from ngsxfem_b200 import _lib
+    if not os.path.exists(_lib.LIB_PATH):
+        import __graft_entry__ as g
+        g.build()
+    return _lib.load()
+
+
+def test_exports_every_declared_symbol(lib):
+    from ngsxfem_b200 import _lib
+    hdr = open(os.path.join(ROOT, "include", "ngsx_abi.h")).read()
+    hdr = re.sub(r"/\*.*?\*/", "", hdr, flags=re.S)
+    declared = set(re.findall(r"\b(ngsx_[a-z0-9_]+)\s*\(", hdr))
+    assert len(declared) >= 25
+    for name in declared:
+        assert hasattr(lib, name), f"{name} declared in include/ngsx_abi.h but not exported"
+    assert declared == set(_lib.SIGNATURES), declared ^ set(_lib.SIGNATURES)
+    assert lib.ngsx_abi_version() == 1
+
+
+def test_no_oracle_in_product():
+    """the product must never import / link the oracle"""
+    for dirpath, _, files in os.walk(os.path.join(ROOT, "ngsxfem_b200")):
+        for f in files:
+            if f.endswith((".py", ".cu", ".cuh", ".h")):
+                txt = open(os.path.join(dirpath, f)).read()
+                assert "import oracle" not in txt and "from oracle" not in txt and "ngsx_oracle" not in txt, f
+
+
+def test_struct_layouts(lib):
+    from ngsxfem_b200 import _lib
+    assert ctypes.sizeof(_lib.Mesh) == 40
+    assert ctypes.sizeof(_lib.FormH1) == 40
+    assert ctypes.sizeof(_lib.Poly) == 8 + 8 * 8 + 8 * 3 * 4
+
+
+def test_argument_errors_are_statuses(lib):
+    from ngsxfem_b200 import _lib
+    m = _lib.Mesh(5, 0, 1, 1, None, None)
+    assert lib.ngsx_classify(ctypes.byref(m), None, None, None, None, None, None) == -1
+    assert b"dim" in lib.ngsx_last_error()
+    with pytest.raises(_lib.NgsxError):
+        _lib.check(lib.ngsx_slot_map(-1, 3, None, None, None, None, None))
+    with pytest.raises(_lib.NgsxError):
+        _lib.make_poly([(1.0, 0.5, 0, 0)])
+
+
+@pytest.mark.parametrize("group", [1, 4, 6])
+def test_color_groups_host(lib, group):
+    from ngsxfem_b200 import meshes
+    m = meshes.MakeStructured3DMesh(5)
+    e2d, ndof = m.h1_dofs(2)
+    tab = e2d.contiguous()
+    n, nd = tab.shape
+    perm = torch.empty(n, dtype=torch.int64)
+    cptr = torch.zeros(257, dtype=torch.int64)
+    nc = ctypes.c_int32(0)
+    assert lib.ngsx_color_groups(n, nd, tab.data_ptr(), ndof, group, perm.data_ptr(), cptr.data_ptr(), 256, ctypes.byref(nc)) == 0
+    nc = nc.value
+    cp = cptr[: nc + 1].numpy()
+    assert cp[0] == 0 and cp[-1] == n and (np.diff(cp) > 0).all()
+    assert np.array_equal(np.sort(perm.numpy()), np.arange(n))                     # a permutation
+    t = tab.numpy()[perm.numpy()]
+    for c in range(nc):
+        seg = t[cp[c]:cp[c + 1]]
+        ng = (len(seg) + group - 1) // group
+        owner = {}
+        for g in range(ng):                                                        # the kernel's windows inside a colour
+            for d in np.unique(seg[g * group:(g + 1) * group]):
+                assert owner.setdefault(d, g) == g, "two groups of one colour share a dof"
+    if group == 1:
+        assert nc >= 24          # a Kuhn-mesh vertex is shared by up to 24 tets
+    # too small capacity is reported, not overrun
+    nc2 = ctypes.c_int32(0)
+    assert lib.ngsx_color_groups(n, nd, tab.data_ptr(), ndof, group, perm.data_ptr(), cptr.data_ptr(), 2, ctypes.byref(nc2)) == -5
+
+
+def test_host_mirror_parses_tutorial_forms():
+    from ngsxfem_b200 import _lib, xfem
+    from ngsxfem_b200.ngs import Expr, LevelsetNormal, grad, specialcf, x, y
+    u, v = Expr.atom("u"), Expr.atom("v")
+    h, n = specialcf.mesh_size, LevelsetNormal()
+    b = xfem.SymbolicCutBFI(None, domain_type=xfem.NEG, form=grad(u) * grad(v))
+    assert (b.form.c_stiff, b.form.c_mass, b.intorder(2), b.intorder(3)) == (1.0, 0.0, 2, 4)    # symboliccutbfi.cpp:97-107
+    b = xfem.SymbolicCutBFI(None, domain_type=xfem.NEG, form=grad(u) * grad(v) + u * v)
+    assert b.intorder(2) == 4
+    b = xfem.SymbolicCutBFI(None, domain_type=xfem.NEG, form=u * v, force_intorder=7)
+    assert b.intorder(2) == 7
+    nit = -grad(u) * n * v - grad(v) * n * u + (90 / h) * u * v                                 # fictdom_ghostpen.py:88-93
+    b = xfem.SymbolicCutBFI(None, domain_type=xfem.IF, form=nit)
+    assert (b.form.c_nitsche, b.form.c_mass, b.form.hpow_mass) == (-1.0, 90.0, -1)
+    gp = xfem.SymbolicFacetPatchBFI(form=0.1 * 1.0 / h * 1.0 / h * (u - u.Other()) * (v - v.Other()), skeleton=False)
+    assert (gp.coef, gp.hpow) == (0.1, -2)
+    lf = xfem.SymbolicCutLFI(None, form=(1 + 2 * x * y) * v)
+    assert lf.coef.terms == {(0, 0, 0): 1.0, (1, 1, 0): 2.0} and lf.intorder(2) == 4
+    for bad in (lambda: xfem.SymbolicCutBFI(None, form=grad(u) * n * v),                        # unsymmetric Nitsche: unsupported -> error
+                lambda: xfem.SymbolicCutBFI(None, form=u * v, element_boundary=True),
+                lambda: xfem.SymbolicCutBFI(None, form=u * v, time_order=2),
+                lambda: xfem.SymbolicFacetPatchBFI(form=u * v, skeleton=False),
+                lambda: xfem.SymbolicFacetPatchBFI(form=(u - u.Other()) * (v - v.Other()), skeleton=True),
+                lambda: xfem.SymbolicCutLFI(None, form=u * v)):
+        with pytest.raises(_lib.NgsxError):
+            bad()
+    assert (xfem.NEG, xfem.POS, xfem.IF) == (0, 1, 2) and int(xfem.HASNEG) == 5 and int(xfem.ANY) == 7   # utils/ngsxstd.hpp

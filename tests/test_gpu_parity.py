@@ -1,0 +1,408 @@
+"""Parity of the CUDA path (through the C ABI, libngsx_b200.so) against the committed golden vectors of the compiled
+reference and against the CPU oracle on the same seeded inputs.  Flags and point counts bit-exact; points, weights,
+element matrices, CSR values and integrals within 1e-12 relative (the north-star tolerance)."""
+import ctypes
+
+import numpy as np
+import pytest
+import torch
+
+pytestmark = pytest.mark.gpu
+
+RTOL = 1e-12
+NEG, POS, IF = 0, 1, 2
+
+
+@pytest.fixture(scope="module")
+def X():
+    from ngsxfem_b200 import _lib, meshes, ngs, xfem
+    assert torch.cuda.is_available()
+    _lib.load()
+
+    class NS:
+        pass
+    ns = NS()
+    ns.lib, ns.meshes, ns.ngs, ns.xfem = _lib, meshes, ngs, xfem
+    return ns
+
+
+def dev(a, dtype=None):
+    t = torch.as_tensor(np.ascontiguousarray(a))
+    if dtype is not None:
+        t = t.to(dtype)
+    return t.cuda().contiguous()
+
+
+def soup_mesh(X, pm, ls):
+    """n independent elements as one mesh (vertex soup): vert [n*(d+1)][d], el2v = arange"""
+    n, nvl, dim = pm.shape
+    m = X.meshes.SimplexMesh(dim, torch.as_tensor(pm.reshape(-1, dim).copy()), torch.arange(n * nvl, dtype=torch.int32).reshape(n, nvl))
+    mesh = X.ngs.Mesh(m)
+    gf = X.ngs.GridFunction(X.ngs.H1(mesh, order=1))
+    gf.vec.copy_(dev(ls.reshape(-1)))
+    return mesh, gf
+
+
+def relerr_rows(a, b):
+    a = a.reshape(len(a), -1); b = b.reshape(len(b), -1)
+    scale = np.maximum(np.abs(b).max(axis=1), 1e-300)
+    return (np.abs(a - b).max(axis=1) / scale).max() if len(a) else 0.0
+
+
+@pytest.mark.parametrize("dim", [2, 3])
+def test_classify_single_elements(X, golden_single, dim):
+    g = golden_single
+    pm, ls = g[f"d{dim}_pmat"], g[f"d{dim}_lset"]
+    mesh, gf = soup_mesh(X, pm, ls)
+    ci = X.xfem.CutInfo(mesh, gf)
+    dom = ci.dom.cpu().numpy()
+    gd = g[f"d{dim}_dom"]
+    # reference throws (-2) <-> kernel flags degenerate (-1)
+    assert np.array_equal(np.where(gd == -2, -1, gd), dom)
+    ok = gd >= 0
+    assert np.abs(ci.ratio.cpu().numpy()[ok] - g[f"d{dim}_ratio"][ok]).max() <= 1e-12
+    nerr, first = ci.err.tolist()
+    assert nerr == int((gd == -2).sum()) and first == int(np.nonzero(gd == -2)[0][0])
+    with pytest.raises(X.lib.NgsxError):
+        ci.check_degenerate()
+    # bit arrays follow the flags (BitArray bit order)
+    for dt, cdt in ((NEG, X.xfem.CDOM_NEG), (POS, X.xfem.CDOM_POS), (IF, X.xfem.CDOM_IF)):
+        assert np.array_equal(ci.GetElementsOfType(cdt).to_bool().cpu().numpy(), dom == dt)
+    assert np.array_equal(ci.GetElementsOfType(X.xfem.HASNEG).to_bool().cpu().numpy(), (dom == NEG) | (dom == IF))
+    assert np.array_equal(ci.GetElementsOfType(X.xfem.UNCUT).to_bool().cpu().numpy(), (dom == NEG) | (dom == POS))
+    assert ci.GetElementsOfType(X.xfem.ANY).NumSet() == len(dom) and ci.GetElementsOfType(X.xfem.NO).NumSet() == 0
+
+
+@pytest.mark.parametrize("dim", [2, 3])
+@pytest.mark.parametrize("dt", [NEG, POS, IF])
+def test_cut_rules_single_elements(X, golden_single, dim, dt):
+    g = golden_single
+    pm, ls = g[f"d{dim}_pmat"], g[f"d{dim}_lset"]
+    mesh, gf = soup_mesh(X, pm, ls)
+    L = X.lib.load()
+    n = mesh.ne
+    st = torch.cuda.current_stream().cuda_stream
+    for order in (0, 1, 2, 3, 4, 5, 6):
+        gn = g[f"d{dim}_dt{dt}_o{order}_npts"]
+        npts = torch.zeros(n, dtype=torch.int32, device="cuda")
+        X.lib.check(L.ngsx_rule_count(ctypes.byref(mesh.c_struct()), gf.vec.data_ptr(), dt, order, npts.data_ptr(), None, st))
+        # reference: -1 = nullptr (0 here); -2 = throw (degenerate: 0 points here, flagged by classify)
+        assert np.array_equal(npts.cpu().numpy(), np.maximum(gn, 0))            # bit-exact counts
+        offs = torch.zeros(n + 1, dtype=torch.int64, device="cuda")
+        X.lib.check(L.ngsx_exclusive_scan(n, npts.data_ptr(), offs.data_ptr(), st))
+        total = int(offs[-1].item())
+        assert total == int(np.maximum(gn, 0).sum())
+        pts = torch.zeros((total, 3), dtype=torch.float64, device="cuda")
+        wts = torch.zeros(total, dtype=torch.float64, device="cuda")
+        X.lib.check(L.ngsx_rule_fill(ctypes.byref(mesh.c_struct()), gf.vec.data_ptr(), dt, order, 1, 1, offs.data_ptr(),
+                                     pts.data_ptr(), wts.data_ptr(), st))
+        P, W = g[f"d{dim}_dt{dt}_o{order}_pts"], g[f"d{dim}_dt{dt}_o{order}_wts"]
+        assert np.abs(pts.cpu().numpy() - P).max() <= 1e-14
+        o = offs.cpu().numpy()
+        w = wts.cpu().numpy()
+        for t in range(n):
+            if gn[t] > 0:
+                a, b = w[o[t]:o[t + 1]], W[o[t]:o[t + 1]]
+                assert np.abs(a - b).max() <= RTOL * np.abs(b).max(), (t, order)
+
+
+@pytest.mark.parametrize("dim", [2, 3])
+@pytest.mark.parametrize("fo", [1, 2])
+@pytest.mark.parametrize("fast", [0, 1])
+def test_elmat_elvec_single_elements(X, golden_single, dim, fo, fast):
+    g = golden_single
+    pm, ls = g[f"d{dim}_pmat"], g[f"d{dim}_lset"]
+    mesh, gf = soup_mesh(X, pm, ls)
+    L = X.lib.load()
+    L.ngsx_debug_set_fast_path(fast)
+    try:
+        n = mesh.ne
+        nd = {(2, 1): 3, (2, 2): 6, (3, 1): 4, (3, 2): 10}[(dim, fo)]
+        st = torch.cuda.current_stream().cuda_stream
+        form = X.lib.FormH1(1.25, 0.75, 0.0, 0, 0, 0, 0)
+        poly = X.lib.make_poly([(1.0, 0, 0, 0), (2.0, 1, 2, 0), (-0.5, 0, 0, 1)])
+        for dt in (NEG, POS, IF):
+            em = torch.full((n, nd, nd), 7.0, dtype=torch.float64, device="cuda")
+            npts = torch.zeros(n, dtype=torch.int32, device="cuda")
+            X.lib.check(L.ngsx_elmat_h1(ctypes.byref(mesh.c_struct()), gf.vec.data_ptr(), fo, dt, 2 * fo, ctypes.byref(form), n, None,
+                                        em.data_ptr(), npts.data_ptr(), st))
+            gn = g[f"d{dim}_p{fo}_dt{dt}_npts"]
+            assert np.array_equal(npts.cpu().numpy(), np.maximum(gn, 0))
+            assert relerr_rows(em.cpu().numpy(), g[f"d{dim}_p{fo}_dt{dt}_elmat"]) <= RTOL
+            ev = torch.full((n, nd), 7.0, dtype=torch.float64, device="cuda")
+            X.lib.check(L.ngsx_elvec_h1(ctypes.byref(mesh.c_struct()), gf.vec.data_ptr(), fo, dt, 2 * fo, ctypes.byref(poly), n, None,
+                                        ev.data_ptr(), npts.data_ptr(), st))
+            ge = g[f"d{dim}_p{fo}_dt{dt}_elvec"]
+            scale = np.maximum(np.abs(g[f"d{dim}_p{fo}_dt{dt}_elmat"]).reshape(n, -1).max(axis=1), np.abs(ge).max(axis=1))
+            assert (np.abs(ev.cpu().numpy() - ge).max(axis=1) <= RTOL * np.maximum(scale, 1e-300)).all()
+    finally:
+        L.ngsx_debug_set_fast_path(1)
+
+
+def _golden_mesh(X, tag, g):
+    if tag == "m3":
+        m = X.meshes.MakeStructured3DMesh(6)
+    else:
+        m = X.meshes.MakeStructured2DMesh(12, lo=(-1, -1), hi=(1, 1))
+    mesh = X.ngs.Mesh(m)
+    gf = X.ngs.GridFunction(X.ngs.H1(mesh, order=1))
+    gf.vec.copy_(dev(g[f"{tag}_lset"]))
+    return mesh, gf
+
+
+@pytest.mark.parametrize("tag", ["m2", "m3"])
+def test_small_mesh_against_reference_golden(X, golden_meshes, tag):
+    g = golden_meshes
+    mesh, gf = _golden_mesh(X, tag, g)
+    x, y, z = X.ngs.x, X.ngs.y, X.ngs.z
+    ci = X.xfem.CutInfo(mesh, gf)
+    assert np.array_equal(ci.dom.cpu().numpy(), g[f"{tag}_dom"])
+    assert np.abs(ci.ratio.cpu().numpy() - g[f"{tag}_ratio"]).max() <= 1e-12
+    for dt in (NEG, POS, IF):
+        ld = {"levelset": gf, "domain_type": dt}
+        for order in (0, 2, 4):
+            ref = g[f"{tag}_int_dt{dt}_o{order}"]
+            v = X.xfem.Integrate(levelset_domain=ld, cf=1.0, mesh=mesh, order=order)
+            assert abs(v - ref[0]) <= RTOL * abs(ref[0])
+            cf2 = x * x + 0.5 * y * (z if mesh.dim == 3 else 1.0)
+            v2 = X.xfem.Integrate(levelset_domain=ld, cf=cf2, mesh=mesh, order=order)
+            assert abs(v2 - ref[1]) <= RTOL * abs(ref[1])
+        for fo in (1, 2):
+            Vh = X.ngs.H1(mesh, order=fo)
+            u, v = Vh.TnT()
+            a = X.xfem.BilinearForm(Vh)
+            a += X.xfem.SymbolicBFI(levelset_domain=ld, form=X.ngs.grad(u) * X.ngs.grad(v) + u * v)
+            els, em, npts = a.elmats(0)
+            gm, gn = g[f"{tag}_p{fo}_dt{dt}_elmat"], g[f"{tag}_p{fo}_dt{dt}_npts"]
+            e = els.cpu().numpy()
+            assert np.array_equal(np.nonzero(gn > 0)[0], e)                       # same set of contributing elements
+            assert np.array_equal(npts.cpu().numpy(), gn[e])                      # bit-exact point counts
+            assert relerr_rows(em.cpu().numpy(), gm[e]) <= RTOL
+
+
+@pytest.mark.parametrize("dim,nx", [(2, 24), (3, 9)])
+@pytest.mark.parametrize("fo", [1, 2])
+@pytest.mark.parametrize("dt", [NEG, POS, IF])
+@pytest.mark.parametrize("group", [1, 6])
+def test_assemble_csr_against_oracle(X, dim, nx, fo, dt, group):
+    from oracle import orc
+    m = X.meshes.MakeStructured2DMesh(nx) if dim == 2 else X.meshes.MakeStructured3DMesh(nx)
+    mesh = X.ngs.Mesh(m)
+    gf = X.ngs.GridFunction(X.ngs.H1(mesh, order=1))
+    c = (0.5,) * dim
+    X.xfem.InterpolateToP1(X.ngs.SphereLevelset(c, 0.35), gf)
+    rng = np.random.default_rng(20241104)
+    gf.vec += dev(1e-3 * rng.uniform(-1, 1, mesh.nv))
+    Vh = X.ngs.H1(mesh, order=fo)
+    u, v = Vh.TnT()
+    a = X.xfem.BilinearForm(Vh)
+    a.group_size = group
+    a += X.xfem.SymbolicBFI(levelset_domain={"levelset": gf, "domain_type": dt}, form=0.7 * X.ngs.grad(u) * X.ngs.grad(v) + 1.3 * u * v)
+    a.Assemble()
+    first = a.mat.vals.clone()
+    a.Assemble()                                                                   # bitwise reproducible (no FP atomics)
+    assert torch.equal(first, a.mat.vals)
+    el2v, vert, ls = mesh.el2v.cpu().numpy(), mesh.vert.cpu().numpy(), gf.vec.cpu().numpy()
+    els = np.arange(mesh.ne, dtype=np.int32)
+    vals, nass = orc.assemble_csr(dim, el2v, vert, ls, fo, Vh.el2dof.cpu().numpy(), dt, a.integrators[0].intorder(fo), 1.3, 0.7,
+                                  np.array([0, mesh.ne]), els, a.mat.rowptr.cpu().numpy(), a.mat.colidx.cpu().numpy(), nthreads=1)
+    assert nass == a._plans[0].els.numel()
+    got = a.mat.vals.cpu().numpy()
+    assert np.abs(got - vals).max() <= RTOL * np.abs(vals).max()
+    # the sparsity is the full element graph: same pattern as scipy's from the dof table
+    import scipy.sparse as sp
+    e2d = Vh.el2dof.cpu().numpy()
+    nd = e2d.shape[1]
+    rows = np.repeat(e2d, nd, axis=1).reshape(-1); cols = np.tile(e2d, (1, nd)).reshape(-1)
+    patt = sp.csr_matrix((np.ones(len(rows)), (rows, cols)), shape=(Vh.ndof, Vh.ndof))
+    patt.sum_duplicates(); patt.sort_indices()
+    assert np.array_equal(patt.indptr, a.mat.rowptr.cpu().numpy()) and np.array_equal(patt.indices, a.mat.colidx.cpu().numpy())
+
+
+def test_linear_form_against_oracle(X):
+    from oracle import orc
+    mesh = X.ngs.Mesh(X.meshes.MakeStructured3DMesh(7))
+    gf = X.ngs.GridFunction(X.ngs.H1(mesh, order=1))
+    X.xfem.InterpolateToP1(X.ngs.SphereLevelset((0.5, 0.5, 0.5), 0.35), gf)
+    x, y, z = X.ngs.x, X.ngs.y, X.ngs.z
+    for fo in (1, 2):
+        Vh = X.ngs.H1(mesh, order=fo)
+        u, v = Vh.TnT()
+        for dt in (NEG, IF):
+            f = X.xfem.LinearForm(Vh)
+            f += X.xfem.SymbolicLFI(levelset_domain={"levelset": gf, "domain_type": dt}, form=(1 + 2 * x * y * y - 0.5 * z) * v)
+            f.Assemble()
+            ref = orc.assemble_vec(3, mesh.el2v.cpu().numpy(), mesh.vert.cpu().numpy(), gf.vec.cpu().numpy(), fo, Vh.el2dof.cpu().numpy(),
+                                   Vh.ndof, dt, 2 * fo, [(1.0, 0, 0, 0), (2.0, 1, 2, 0), (-0.5, 0, 0, 1)])
+            assert np.abs(f.vec.cpu().numpy() - ref).max() <= RTOL * np.abs(ref).max()
+
+
+def test_nitsche_form_2d_against_oracle_elmat(X):
+    """IF form of py_tutorials/fictdom_ghostpen.py:88-93: -grad(u).n v - grad(v).n u + (lambda/h) u v, checked per element with the
+    oracle's quadrature points (independent assembly in numpy)."""
+    from oracle import orc
+    mesh = X.ngs.Mesh(X.meshes.MakeStructured2DMesh(10, lo=(-1, -1), hi=(1, 1)))
+    gf = X.ngs.GridFunction(X.ngs.H1(mesh, order=1))
+    X.xfem.InterpolateToP1(X.ngs.RingLevelset((0, 0), 0.25, 0.75), gf)
+    for fo in (1, 2):
+        Vh = X.ngs.H1(mesh, order=fo)
+        u, v = Vh.TnT()
+        n, h = X.ngs.LevelsetNormal(gf), X.ngs.specialcf.mesh_size
+        lam = 10.0 * fo * fo
+        a = X.xfem.BilinearForm(Vh)
+        a += X.xfem.SymbolicBFI(levelset_domain={"levelset": gf, "domain_type": IF},
+                                form=-X.ngs.grad(u) * n * v - X.ngs.grad(v) * n * u + (lam / h) * u * v)
+        els, em, npts = a.elmats(0)
+        em = em.cpu().numpy()
+        el2v, vert, ls = mesh.el2v.cpu().numpy(), mesh.vert.cpu().numpy(), gf.vec.cpu().numpy()
+        assert a.integrators[0].intorder(fo) == 2 * fo
+        for k, e in enumerate(els.cpu().numpy()):
+            pm = vert[el2v[e]]; l = ls[el2v[e]]
+            npt, pts, w = orc.cut_rule(2, pm, l, IF, 2 * fo)
+            assert npt == npts[k].item()
+            J = (pm[:2] - pm[2]).T
+            Jinv = np.linalg.inv(J); meas = abs(np.linalg.det(J)); hh = meas ** 0.5
+            gphi = Jinv.T @ (l[:2] - l[2]); nn = gphi / np.linalg.norm(gphi)
+            ref = np.zeros_like(em[k])
+            for q in range(npt):
+                s, ds = orc.h1_shape(2, fo, el2v[e], pts[q, :2])
+                g = ds @ Jinv
+                gn = g @ nn
+                ref += meas * w[q] * (-(np.outer(s, gn) + np.outer(gn, s)) + lam / hh * np.outer(s, s))
+            assert np.abs(em[k] - ref).max() <= 1e-11 * np.abs(ref).max()
+
+
+def test_facet_marking_and_patches(X):
+    from oracle import orc
+    mesh = X.ngs.Mesh(X.meshes.MakeStructured2DMesh(12, lo=(-1, -1), hi=(1, 1)))
+    gf = X.ngs.GridFunction(X.ngs.H1(mesh, order=1))
+    X.xfem.InterpolateToP1(X.ngs.RingLevelset((0, 0), 0.25, 0.75), gf)
+    ci = X.xfem.CutInfo(mesh, gf)
+    hasneg, hasif = ci.GetElementsOfType(X.xfem.HASNEG), ci.GetElementsOfType(IF)
+    ba = X.xfem.GetFacetsWithNeighborTypes(mesh, a=hasneg, b=hasif)
+    _, f2e = mesh.facets()
+    f2e_h = f2e.cpu().numpy()
+    ref = orc.facets_neighbor_types(f2e_h, hasneg.to_bool().cpu().numpy(), hasif.to_bool().cpu().numpy())
+    assert np.array_equal(ba.to_bool().cpu().numpy(), ref)
+    ref_or = orc.facets_neighbor_types(f2e_h, hasneg.to_bool().cpu().numpy(), hasif.to_bool().cpu().numpy(), False, True, False)
+    ba_or = X.xfem.GetFacetsWithNeighborTypes(mesh, a=hasneg, b=hasif, bnd_val_a=False, bnd_val_b=True, use_and=False)
+    assert np.array_equal(ba_or.to_bool().cpu().numpy(), ref_or)
+    els = X.xfem.GetElementsWithNeighborFacets(mesh, ba)
+    assert np.array_equal(els.to_bool().cpu().numpy(), orc.elements_with_neighbor_facets(f2e_h, mesh.ne, ref))
+    for fo in (1, 2):
+        Vh = X.ngs.H1(mesh, order=fo, dgjumps=True)
+        dofs = X.xfem.GetDofsOfElements(Vh, hasneg)
+        assert np.array_equal(dofs.to_bool().cpu().numpy(), orc.dofs_of_elements(Vh.el2dof.cpu().numpy(), Vh.ndof, hasneg.to_bool().cpu().numpy()))
+        # ghost penalty patch matrices vs the oracle, and the assembled operator vs a scipy assembly of the oracle's blocks
+        u, v = Vh.TnT()
+        h = X.ngs.specialcf.mesh_size
+        a = X.xfem.RestrictedBilinearForm(Vh, element_restriction=hasneg, facet_restriction=ba)
+        a += X.xfem.SymbolicFacetPatchBFI(form=0.1 * 1.0 / h * 1.0 / h * (u - u.Other()) * (v - v.Other()), skeleton=False, definedonelements=ba)
+        a.Assemble()
+        import scipy.sparse as sp
+        el2v, vert, e2d = mesh.el2v.cpu().numpy(), mesh.vert.cpu().numpy(), Vh.el2dof.cpu().numpy()
+        A = sp.lil_matrix((Vh.ndof, Vh.ndof))
+        for f in np.nonzero(ref)[0]:
+            e0, e1 = f2e_h[f]
+            if e1 < 0:
+                continue
+            _, em = orc.facetpatch_elmat_h1(2, fo, el2v[e0], vert[el2v[e0]], el2v[e1], vert[el2v[e1]], 0.1, -2)
+            d = np.concatenate([e2d[e0], e2d[e1]])
+            for i in range(len(d)):
+                for j in range(len(d)):
+                    A[d[i], d[j]] += em[i, j]
+        diff = abs(a.mat.to_scipy() - A.tocsr()).max()
+        assert diff <= 1e-11 * abs(A).max()
+
+
+def test_unsupported_paths_raise(X):
+    mesh = X.ngs.Mesh(X.meshes.MakeStructured2DMesh(2))
+    gf = X.ngs.GridFunction(X.ngs.H1(mesh, order=1))
+    with pytest.raises(X.lib.NgsxError):
+        X.xfem.Integrate(levelset_domain={"levelset": gf, "domain_type": IF, "subdivlvl": 2}, cf=1.0, mesh=mesh, order=2)
+    with pytest.raises(X.lib.NgsxError):
+        X.xfem.CutInfo(mesh, gf, time_order=2)
+    with pytest.raises(X.lib.NgsxError):
+        X.xfem.Integrate(levelset_domain={"levelset": gf, "domain_type": IF}, cf=1.0, mesh=mesh, order=40)   # rule not tabulated
+    gf.vec.zero_()                                                                                          # all-zero level set: reference throws
+    ci = X.xfem.CutInfo(mesh, gf)
+    with pytest.raises(X.lib.NgsxError):
+        ci.check_degenerate()
+
+
+def test_reference_kats_on_gpu(X):
+    """the reference's analytic tests (tests/pytests/test_straightcutrule.py:111-126, 191-207; test_localgeom.py:24-45)"""
+    from math import sqrt
+    x, y, z = X.ngs.x, X.ngs.y, X.ngs.z
+    for N in (1, 10, 30):
+        mesh = X.ngs.Mesh(X.meshes.MakeStructured2DMesh(N))
+        gf = X.ngs.GridFunction(X.ngs.H1(mesh, order=1))
+        X.xfem.InterpolateToP1(1 - 2 * x - 2 * y, gf)
+        for order in (2, 4, 8):
+            for dt, ref in ((NEG, 7 / 8), (POS, 1 / 8), (IF, 1 / sqrt(2))):
+                val = X.xfem.Integrate(levelset_domain={"levelset": gf, "domain_type": dt}, cf=1.0, mesh=mesh, order=order)
+                assert abs(val - ref) < 5e-15 * (order + 1) ** 2
+    mesh = X.ngs.Mesh(X.meshes.MakeStructured3DMesh(1))
+    gf = X.ngs.GridFunction(X.ngs.H1(mesh, order=1))
+    X.xfem.InterpolateToP1(1 - 2 * x - 2 * y - 2 * z, gf)
+    for order in (2, 4, 8):
+        for dt, ref in ((POS, 1 / 48), (NEG, 47 / 48), (IF, sqrt(3) / 8)):
+            val = X.xfem.Integrate(levelset_domain={"levelset": gf, "domain_type": dt}, cf=1.0, mesh=mesh, order=order)
+            assert abs(val - ref) < 5e-15 * (order + 1) ** 2
+    vert = torch.tensor([[0, 0], [1, 0], [0, 1], [.5, 0], [.5, .5], [0, .5]], dtype=torch.float64)
+    el2v = torch.tensor([[0, 3, 5], [3, 1, 4], [5, 4, 2], [3, 4, 5]], dtype=torch.int32)
+    mesh = X.ngs.Mesh(X.meshes.SimplexMesh(2, vert, el2v))
+    gf = X.ngs.GridFunction(X.ngs.H1(mesh, order=1))
+    X.xfem.InterpolateToP1(x + y - 0.25, gf)
+    for order in range(16):
+        neg = X.xfem.Integrate(levelset_domain={"levelset": gf, "domain_type": NEG}, cf=1.0, mesh=mesh, order=order)
+        pos = X.xfem.Integrate(levelset_domain={"levelset": gf, "domain_type": POS}, cf=1.0, mesh=mesh, order=order)
+        tol = 5e-16 * (order + 1) ** 2
+        assert abs(neg - 1 / 32) < tol and abs(pos - 0.5 + 1 / 32) < tol and abs(neg + pos - 0.5) < tol
+    # XFESpace ndof pin (tests/pytests/test_xfes_ndof.py): dofs of IF elements = 7 (2D) / 35 (3D)
+    mesh = X.ngs.Mesh(X.meshes.MakeStructured2DMesh(4, lo=(-1, -1), hi=(1, 1)))
+    V = X.ngs.H1(mesh, order=1); gf = X.ngs.GridFunction(V)
+    X.xfem.InterpolateToP1(X.ngs.SphereLevelset((0, 0), 1 / 3), gf)
+    assert X.xfem.GetDofsOfElements(V, X.xfem.CutInfo(mesh, gf).GetElementsOfType(IF)).NumSet() == 7
+    mesh = X.ngs.Mesh(X.meshes.MakeStructured3DMesh(4, lo=(-1, -1, -1), hi=(1, 1, 1)))
+    V = X.ngs.H1(mesh, order=1); gf = X.ngs.GridFunction(V)
+    X.xfem.InterpolateToP1(X.ngs.CylinderZLevelset((0, 0), 1 / 3), gf)
+    assert X.xfem.GetDofsOfElements(V, X.xfem.CutInfo(mesh, gf).GetElementsOfType(IF)).NumSet() == 35
+
+
+def test_full_size_properties(X):
+    """config-2 sized mesh (nx=119 -> 10.1M tets): size-independent properties instead of an oracle run:
+    counts of SURVEY.md section 8, partition of unity of the measures, mass-matrix sum = volume, stiffness row sums = 0."""
+    from math import pi
+    nx = 119
+    mesh = X.ngs.Mesh(X.meshes.MakeStructured3DMesh(nx, device="cuda"))
+    gf = X.ngs.GridFunction(X.ngs.H1(mesh, order=1))
+    X.xfem.InterpolateToP1(X.ngs.SphereLevelset((0.5, 0.5, 0.5), 0.35), gf)
+    ci = X.xfem.CutInfo(mesh, gf)
+    ci.check_degenerate()
+    counts = [ci.GetElementsOfType(dt).NumSet() for dt in (NEG, POS, IF)]
+    assert counts == [1739292, 8222544, 149118]                                   # SURVEY.md section 8 (numpy restatement of the sign test)
+    ld = lambda dt: {"levelset": gf, "domain_type": dt}
+    vneg = X.xfem.Integrate(levelset_domain=ld(NEG), cf=1.0, mesh=mesh, order=4)
+    vpos = X.xfem.Integrate(levelset_domain=ld(POS), cf=1.0, mesh=mesh, order=4)
+    area = X.xfem.Integrate(levelset_domain=ld(IF), cf=1.0, mesh=mesh, order=4)
+    assert abs(vneg + vpos - 1.0) < 1e-12
+    assert abs(vneg - 4 / 3 * pi * 0.35 ** 3) < 2e-4 and abs(area - 4 * pi * 0.35 ** 2) < 2e-3      # O(h^2) geometry error
+    assert X.xfem.Integrate(levelset_domain=ld(NEG), cf=1.0, mesh=mesh, order=4) == vneg            # reproducible reduction
+    Vh = X.ngs.H1(mesh, order=2)
+    u, v = Vh.TnT()
+    a = X.xfem.RestrictedBilinearForm(Vh, element_restriction=ci.GetElementsOfType(X.xfem.HASNEG))
+    a += X.xfem.SymbolicBFI(levelset_domain=ld(NEG), form=u * v)
+    a.Assemble()
+    # P2 hierarchical basis: sum_i<4 phi_i = 1 -> the vertex-vertex block of the mass matrix sums to the NEG volume
+    rows = torch.repeat_interleave(torch.arange(Vh.ndof, device="cuda"), a.mat.rowptr[1:] - a.mat.rowptr[:-1])
+    vv = (rows < mesh.nv) & (a.mat.colidx < mesh.nv)
+    assert abs(a.mat.vals[vv].sum().item() - vneg) < 1e-11
+    b = X.xfem.RestrictedBilinearForm(Vh, element_restriction=ci.GetElementsOfType(X.xfem.HASNEG))
+    b += X.xfem.SymbolicBFI(levelset_domain=ld(NEG), form=X.ngs.grad(u) * X.ngs.grad(v))
+    b.Assemble()
+    # constants are in the kernel of the stiffness matrix: K * (1 on vertex dofs, 0 on edge dofs) = 0
+    ones = torch.zeros(Vh.ndof, dtype=torch.float64, device="cuda"); ones[: mesh.nv] = 1.0
+    r = torch.zeros(Vh.ndof, dtype=torch.float64, device="cuda")
+    r.index_add_(0, rows, b.mat.vals * ones[b.mat.colidx.long()])
+    assert r.abs().max().item() < 1e-9 * b.mat.vals.abs().max().item()
