@@ -1,0 +1,349 @@
+#!/usr/bin/env python3
+"""bench.py -- cut-element matrices assembled per second on BASELINE.json's config 2:
+3D unit cube, Kuhn tets (nx=119 -> 10 110 954 tets), sphere level set r=0.35, P2 H1, NEG stiffness+mass assembled to CSR,
+plus CutInfo classification and the IF / NEG Integrate() reductions.
+
+  python bench.py --gpus N --steps K --warmup W            (N > 1: launched by torch.distributed.run, one rank per GPU)
+  python bench.py --impl reference ...                      (the reference's own CPU code, oracle/_ref, on the host cores)
+
+One JSON line on rank 0.  A "step" = CutInfo.Update + BilinearForm.Assemble (SetZero + fused rule/elmat/scatter, colour by
+colour) + Integrate(IF) + Integrate(NEG) on device-resident inputs; `value` = HASNEG elements assembled / step time summed
+over ranks; `e2e` = the same step through the Python surface with the level set coming from pinned host memory and the CSR
+values + integrals going back to the host every step."""
+import argparse
+import ctypes
+import json
+import os
+import statistics
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+ALGO_BYTES_PER_ELEMENT = 1784          # 184 B in + 100 CSR entries x (8 B read + 8 B write)
+ALGO_BYTES_CLASSIFY = 56               # 16 B el2v + 32 B level set + 3 bits + 8 B ratio
+METRIC = "cut-element matrices assembled/sec (3D P2 sphere)"
+
+
+def parse():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--nx", type=int, default=119)
+    ap.add_argument("--group", type=int, default=6)
+    ap.add_argument("--cpu-seconds", type=float, default=12.0, help="target CPU time of the cpu_baseline sample")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    return ap.parse_args()
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons DURING the timed region (B200_PROFILING.md recipe)"""
+    Q = "clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown," \
+        "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap"
+
+    def __init__(self, index):
+        self.proc, self.lines, self.index = None, [], index
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.index), f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-lms", "100"],
+                                         stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            threading.Thread(target=self._read, daemon=True).start()
+        except OSError:
+            self.proc = None
+
+    def _read(self):
+        for ln in self.proc.stdout:
+            self.lines.append(ln.strip())
+
+    def stop(self):
+        if self.proc is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.15)
+        self.proc.kill()
+        self.proc.wait()
+        sm, smax, reasons = [], None, set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for ln in self.lines:
+            f = [x.strip() for x in ln.split(",")]
+            if len(f) < 7:
+                continue
+            try:
+                sm.append(float(f[0])); smax = float(f[1])
+            except ValueError:
+                continue
+            for n, v in zip(names, f[3:7]):
+                if v.lower().startswith("active"):
+                    reasons.add(n)
+        return {"sm_mhz": statistics.median(sm) if sm else None, "sm_max_mhz": smax, "reasons": sorted(reasons), "samples": len(sm)}
+
+
+def measured_peak():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        return float(json.load(open(p))["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs)"
+    return 6650.0, "fallback (B200_PROFILING.md)"
+
+
+# ======================================================================================================================
+def build_problem(nx, device, rank=0, world=1, group=6):
+    import torch
+    from ngsxfem_b200 import meshes, xfem
+    from ngsxfem_b200.ngs import GridFunction, H1, Mesh, SphereLevelset, grad
+    mesh = Mesh(meshes.MakeStructured3DMesh(nx, device=device), device=device)
+    lsetp1 = GridFunction(H1(mesh, order=1))
+    xfem.InterpolateToP1(SphereLevelset((0.5, 0.5, 0.5), 0.35), lsetp1)
+    ci = xfem.CutInfo(mesh, lsetp1)
+    ci.check_degenerate()
+    Vh = H1(mesh, order=2)
+    hasneg = ci.GetElementsOfType(xfem.HASNEG)
+    active = hasneg.nonzero()
+    n_total = active.numel()
+    if world > 1:                                       # contiguous block of the active list per rank (slab in cube-major order)
+        lo, hi = rank * n_total // world, (rank + 1) * n_total // world
+        mine = torch.zeros(mesh.ne, dtype=torch.bool, device=device)
+        mine[active[lo:hi]] = True
+        from ngsxfem_b200.ngs import BitArray
+        restr = BitArray.from_bool(mine)
+    else:
+        restr = hasneg
+    u, v = Vh.TnT()
+    a = xfem.RestrictedBilinearForm(Vh, element_restriction=restr)
+    a.group_size = group
+    a += xfem.SymbolicBFI(levelset_domain={"levelset": lsetp1, "domain_type": xfem.NEG}, form=grad(u) * grad(v) + u * v,
+                          definedonelements=restr)
+    return dict(mesh=mesh, lsetp1=lsetp1, ci=ci, Vh=Vh, a=a, n_total=n_total, xfem=xfem)
+
+
+def run_b200(args):
+    import torch
+    import torch.distributed as dist
+    rank = int(os.environ.get("RANK", 0)); world = int(os.environ.get("WORLD_SIZE", 1)); lrank = int(os.environ.get("LOCAL_RANK", 0))
+    assert torch.cuda.is_available(), "bench.py needs a CUDA device: the CUDA library is the product, there is no CPU fallback"
+    torch.cuda.set_device(lrank)
+    dev = f"cuda:{lrank}"
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device(dev))
+    import __graft_entry__ as ge
+    if rank == 0:
+        ge.build()
+    if world > 1:
+        dist.barrier()
+    from ngsxfem_b200 import _lib
+    L = _lib.load()
+    t0 = time.time()
+    P = build_problem(args.nx, dev, rank, world, args.group)
+    mesh, lsetp1, ci, a, xfem = P["mesh"], P["lsetp1"], P["ci"], P["a"], P["xfem"]
+    a.Assemble()                                         # symbolic phase (graph, colouring, slot map) + first numeric pass
+    torch.cuda.synchronize()
+    setup_s = time.time() - t0
+    plan = a._plans[0]
+    n_local = plan.els.numel()
+    ld_if = {"levelset": lsetp1, "domain_type": xfem.IF}
+    ld_neg = {"levelset": lsetp1, "domain_type": xfem.NEG}
+
+    ev = lambda: torch.cuda.Event(enable_timing=True)
+    stage_ms = {"classify": [], "assemble": [], "integrate": []}
+
+    def step(record):
+        e = [ev() for _ in range(4)]
+        e[0].record()
+        ci.Update(lsetp1)
+        e[1].record()
+        a.Assemble()
+        e[2].record()
+        s_if = xfem.IntegrateX(lsetp1, mesh, cf=1.0, order=4, domain_type=xfem.IF, sync=False)
+        s_neg = xfem.IntegrateX(lsetp1, mesh, cf=1.0, order=4, domain_type=xfem.NEG, sync=False)
+        e[3].record()
+        if record:
+            record.append(e)
+        return s_if, s_neg
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    for _ in range(args.warmup):
+        step(None)
+    barrier()
+    sampler = ClockSampler(lrank)
+    sampler.start()
+    launches0 = L.ngsx_launch_count()
+    rec = []
+    t_begin, t_end = ev(), ev()
+    t_begin.record()
+    for _ in range(args.steps):
+        s_if, s_neg = step(rec)
+        if world > 1:                                    # the path's only exchange at this tier: scalar Integrate() all-reduce
+            sc = torch.cat([s_if, s_neg])
+            dist.all_reduce(sc)
+    t_end.record()
+    barrier()
+    launches = L.ngsx_launch_count() - launches0
+    total_ms = t_begin.elapsed_time(t_end)
+    for e in rec:
+        stage_ms["classify"].append(e[0].elapsed_time(e[1]))
+        stage_ms["assemble"].append(e[1].elapsed_time(e[2]))
+        stage_ms["integrate"].append(e[2].elapsed_time(e[3]))
+
+    # ---- e2e: level set from pinned host memory every step, CSR values + integrals back to the host ----------------
+    h_lset = lsetp1.vec.cpu().pin_memory()
+    h_vals = torch.empty(a.mat.nnz, dtype=torch.float64).pin_memory()
+    h_sc = torch.empty(2, dtype=torch.float64).pin_memory()
+    from ngsxfem_b200.ngs import GridFunction
+    gf_in = GridFunction(lsetp1.space)
+
+    def e2e_step():
+        gf_in.vec.copy_(h_lset, non_blocking=True)                       # H2D: this step's input
+        xfem.InterpolateToP1(gf_in, lsetp1)                              # GridFunction branch + clamp
+        s_if, s_neg = step(None)
+        h_vals.copy_(a.mat.vals, non_blocking=True)                      # D2H: the assembled operator
+        h_sc.copy_(torch.cat([s_if, s_neg]), non_blocking=True)
+        torch.cuda.current_stream().synchronize()
+
+    for _ in range(max(1, args.warmup)):
+        e2e_step()
+    barrier()
+    e_b, e_e = ev(), ev()
+    e_b.record()
+    for _ in range(args.steps):
+        e2e_step()
+    e_e.record()
+    barrier()
+    e2e_ms = e_b.elapsed_time(e_e)
+    clocks = sampler.stop()
+
+    # ---- max over ranks -----------------------------------------------------------------------------------------------
+    t = torch.tensor([total_ms, e2e_ms, statistics.mean(stage_ms["classify"]), statistics.mean(stage_ms["assemble"]),
+                      statistics.mean(stage_ms["integrate"])], dtype=torch.float64, device=dev)
+    cnt = torch.tensor([n_local, a.mat.nnz, launches], dtype=torch.int64, device=dev)
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        dist.all_reduce(cnt, op=dist.ReduceOp.SUM)
+    total_ms, e2e_ms, cl_ms, as_ms, in_ms = t.tolist()
+    n_global, nnz_global, launches_global = cnt.tolist()
+    if rank != 0:
+        if world > 1:
+            dist.destroy_process_group()
+        return
+    ms_per_step = total_ms / args.steps
+    value = n_global / (ms_per_step * 1e-3)
+    peak, peak_src = measured_peak()
+    # dominant kernel = the fused assemble kernel (one launch per colour): algorithmic bytes of this rank's launches / their time
+    as_local = statistics.mean(stage_ms["assemble"])
+    achieved = ALGO_BYTES_PER_ELEMENT * n_local / (as_local * 1e-3) / 1e9
+    traffic = None
+    tp = os.path.join(ROOT, "profiles", "r01_assemble_traffic.json")
+    if os.path.exists(tp):
+        traffic = json.load(open(tp)).get("dram_bytes_per_step")
+    out = {
+        "metric": METRIC, "value": value, "unit": "elements/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
+        "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f64",
+        "data": "synthetic",
+        "config": {"workload": f"configs[1]: 3D unit-cube Kuhn tets nx={args.nx} ({mesh.ne} tets), sphere r=0.35, P2 H1, NEG grad-grad+mass "
+                               f"assemble-to-CSR ({n_global} HASNEG elements) + CutInfo + Integrate(IF,NEG)",
+                   "ne": mesh.ne, "hasneg_elements": n_global, "nnz": nnz_global, "group": args.group, "colors": plan.ncolors,
+                   "setup_s_untimed": round(setup_s, 2), "stage_ms": {"classify": cl_ms, "assemble": as_ms, "integrate": in_ms},
+                   "l2": "inputs larger than L2 (CSR values + slot map > 1 GB per step vs 126 MB L2); no explicit flush",
+                   "partition": "contiguous blocks of the HASNEG element list per rank; Integrate scalars all-reduced (NCCL)"},
+        "roofline": {"bound": "hbm", "kernel": "k_elmat<3,2,CSR> (fused cut rule + element matrix + CSR +=), all colour launches of a step",
+                     "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": traffic,
+                     "peak_source": peak_src, "algorithmic_bytes_per_element": ALGO_BYTES_PER_ELEMENT,
+                     "classify_gbs": ALGO_BYTES_CLASSIFY * mesh.ne / (cl_ms * 1e-3) / 1e9},
+        "e2e": {"value": n_global / (e2e_ms / args.steps * 1e-3), "unit": "elements/s", "h2d_bytes_per_step": int(h_lset.numel() * 8),
+                "d2h_bytes_per_step": int(h_vals.numel() * 8 + 16), "ms_per_step": e2e_ms / args.steps,
+                "note": "mesh, dof table, sparsity and slot map stay resident; per step the level set is uploaded and the CSR values + integrals are downloaded"},
+        "gpu_launches": int(launches_global), "clocks": clocks,
+    }
+    if world == 1 and not args.no_cpu_baseline:
+        try:
+            out["cpu_baseline"] = cpu_baseline(P, args.cpu_seconds, steps=1, warmup=0)[0]
+        except Exception as exc:                        # never lose the GPU line to a host-side problem
+            out["cpu_baseline"] = {"error": str(exc)[:200]}
+    print(json.dumps(out), flush=True)
+    if world > 1:
+        dist.destroy_process_group()
+
+
+# ======================================================================================================================
+def cpu_baseline(P, target_seconds, steps, warmup):
+    """the reference's own CPU code (oracle/_ref: straightcutrule.cpp + NGSolve FE/AddABt compiled in place) or, where that
+    library is absent, the C port (oracle/), on a bounded sample of the same workload: every k-th HASNEG element, all host
+    threads, colour by colour like NGSolve's IterateElements, scattered into the same CSR pattern."""
+    import numpy as np
+    import torch
+    from oracle import orc, refload
+    kind = "reference" if refload.available() else "port"
+    impl = "ref" if kind == "reference" else "oracle"
+    mesh, a, Vh, lsetp1 = P["mesh"], P["a"], P["Vh"], P["lsetp1"]
+    if a.mat is None:
+        a.Assemble()
+    el2v, vert, ls = mesh.el2v.cpu().numpy(), mesh.vert.cpu().numpy(), lsetp1.vec.cpu().numpy()
+    e2d = Vh.el2dof.cpu().numpy()
+    rowptr, colidx = a.mat.rowptr.cpu().numpy(), a.mat.colidx.cpu().numpy()
+    active = a._plans[0].els.cpu().numpy() if 0 in a._plans else None
+    active = np.sort(active)
+    cores = os.cpu_count() or 1
+
+    def run(sample):
+        from ngsxfem_b200 import xfem
+        tab = torch.as_tensor(e2d[sample]).contiguous()
+        perm, cptr = xfem.color_list(tab, Vh.ndof, 1)                 # per-element colouring (NGSolve's)
+        els = sample[perm.numpy()].astype(np.int32)
+        t0 = time.perf_counter()
+        _, nass = orc.assemble_csr(3, el2v, vert, ls, 2, e2d, 0, 4, 1.0, 1.0, np.array(cptr, dtype=np.int64), els, rowptr, colidx,
+                                   impl=impl, nthreads=cores)
+        return time.perf_counter() - t0, nass
+
+    probe = active[:: max(1, len(active) // 20000)]
+    dt, n = run(probe)
+    rate = n / dt
+    nsample = int(min(len(active), max(20000, rate * target_seconds)))
+    sample = active[:: max(1, len(active) // nsample)]
+    res = []
+    for i in range(warmup + steps):
+        dt, n = run(sample)
+        if i >= warmup:
+            res.append((dt, n))
+    tot_t = sum(r[0] for r in res); tot_n = sum(r[1] for r in res)
+    info = {"value": tot_n / tot_t, "unit": "elements/s", "cores": cores, "kind": kind,
+            "sample": f"every {max(1, len(active) // nsample)}-th of the {len(active)} HASNEG elements ({len(sample)} elements, {tot_t / len(res):.1f} s per pass), "
+                      f"rule + P2 element matrix + CSR scatter under a per-element colouring, OpenMP threads = cores"}
+    return info, tot_t / len(res) * 1e3
+
+
+def run_reference(args):
+    rank = int(os.environ.get("RANK", 0))
+    if rank != 0:
+        return
+    import torch
+    import __graft_entry__ as ge
+    ge.build()
+    dev = "cuda:0" if torch.cuda.is_available() else "cpu"
+    if dev == "cpu":
+        raise SystemExit("reference arm: mesh/sparsity setup uses the product's device builders; needs the GPU box")
+    P = build_problem(args.nx, dev, 0, 1, args.group)
+    P["a"].Assemble()
+    info, ms = cpu_baseline(P, args.cpu_seconds, steps=args.steps, warmup=args.warmup)
+    out = {"impl": "reference", "metric": METRIC, "value": info["value"], "unit": "elements/s", "n_gpus": args.gpus, "steps": args.steps,
+           "warmup": args.warmup, "ms_per_step": ms, "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f64",
+           "data": "synthetic",
+           "config": {"workload": f"configs[1]: 3D unit-cube Kuhn tets nx={args.nx}, sphere r=0.35, P2 H1, NEG grad-grad+mass assemble-to-CSR; "
+                                  "each step = one pass over a bounded sample of the HASNEG elements on the host cores"},
+           "cpu_baseline": info,
+           "e2e": {"value": info["value"], "unit": "elements/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
+    print(json.dumps(out), flush=True)
+
+
+if __name__ == "__main__":
+    args = parse()
+    if args.impl == "reference":
+        run_reference(args)
+    else:
+        run_b200(args)
