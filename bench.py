@@ -160,7 +160,7 @@ def run_b200(args):
         s_if = xfem.IntegrateX(lsetp1, mesh, cf=1.0, order=4, domain_type=xfem.IF, sync=False)
         s_neg = xfem.IntegrateX(lsetp1, mesh, cf=1.0, order=4, domain_type=xfem.NEG, sync=False)
         e[3].record()
-        if record:
+        if record is not None:
             record.append(e)
         return s_if, s_neg
 
