@@ -143,7 +143,7 @@ def run_b200(args):
     torch.cuda.synchronize()
     setup_s = time.time() - t0
     plan = a._plans[0]
-    n_local = plan.els.numel()
+    n_local = plan.els.numel()                           # listed elements = HASNEG elements of this rank (restriction)
     ld_if = {"levelset": lsetp1, "domain_type": xfem.IF}
     ld_neg = {"levelset": lsetp1, "domain_type": xfem.NEG}
 
@@ -206,6 +206,7 @@ def run_b200(args):
         h_vals.copy_(a.mat.vals, non_blocking=True)                      # D2H: the assembled operator
         h_sc.copy_(torch.cat([s_if, s_neg]), non_blocking=True)
         torch.cuda.current_stream().synchronize()
+        a.check_degenerate()                                             # the reference throws from inside Assemble; here: after the sync
 
     for _ in range(max(1, args.warmup)):
         e2e_step()
@@ -248,7 +249,7 @@ def run_b200(args):
         "data": "synthetic",
         "config": {"workload": f"configs[1]: 3D unit-cube Kuhn tets nx={args.nx} ({mesh.ne} tets), sphere r=0.35, P2 H1, NEG grad-grad+mass "
                                f"assemble-to-CSR ({n_global} HASNEG elements) + CutInfo + Integrate(IF,NEG)",
-                   "ne": mesh.ne, "hasneg_elements": n_global, "nnz": nnz_global, "group": args.group, "colors": plan.ncolors,
+                   "ne": mesh.ne, "hasneg_elements": n_global, "nnz": nnz_global, "assembly": a.assembly, "group": args.group, "colors": plan.ncolors,
                    "setup_s_untimed": round(setup_s, 2), "stage_ms": {"classify": cl_ms, "assemble": as_ms, "integrate": in_ms},
                    "l2": "inputs larger than L2 (CSR values + slot map > 1 GB per step vs 126 MB L2); no explicit flush",
                    "partition": "contiguous blocks of the HASNEG element list per rank; Integrate scalars all-reduced (NCCL)"},

@@ -161,6 +161,29 @@ int ngsx_assemble_vec_h1(const ngsx_mesh *mesh, const double *lset_v, int fe_ord
                          const ngsx_poly *h_f, int64_t nlist, const int32_t *els, const int32_t *el2dof_list /*[nlist][nd]*/,
                          int32_t ncolors, const int64_t *h_color_ptr, int32_t group, double *vec, void *stream);
 
+/* ---- (d') owner-computes assembly: every CSR row is gathered by one warp, each value is written exactly once ------
+ * Same result as ngsx_assemble_csr_h1 (SetZero + AddElementMatrix over all listed elements, NGS/comp/bilinearform.cpp:986,
+ * 1563 + NGS/linalg/sparsematrix_impl.hpp:63-103) without colouring, zero-fill or read-modify-write: the plan holds, per
+ * CSR row, the (element, local row) pairs contributing to it and the position of each local column inside the row; the
+ * contributions of one entry are summed in list order by a single warp, so the values are bitwise reproducible and no
+ * floating-point atomic is used.  Multi-GPU: a plan restricted to rows [row_lo, row_hi) makes the rank the owner of those
+ * rows -- it recomputes the halo elements listed in `table` instead of exchanging interface rows.
+ * table [nlist][nd]: dofs of list entry k (list order fixes the summation order); rows longer than 256 entries are
+ * NGSX_ERR_UNSUPPORTED (use the coloured path). */
+typedef struct ngsx_rowplan ngsx_rowplan;   /* opaque, owns device buffers (pair descriptors, geometry factors, cut-element matrices) */
+int ngsx_rowplan_create(int64_t nlist, int32_t nd, const int32_t *table, int64_t ndof, const int64_t *rowptr, const int32_t *colidx,
+                        int64_t row_lo, int64_t row_hi, ngsx_rowplan **out, void *stream);
+/* h_info[0..5] = {non-empty rows, (row, element) pairs, CSR entries covered by the plan's rows, longest row, first covered CSR
+ * entry, one past the last covered CSR entry} */
+int ngsx_rowplan_info(const ngsx_rowplan *plan, int64_t *h_info);
+int ngsx_rowplan_destroy(ngsx_rowplan *plan);
+/* els [nlist]: element numbers of the list entries (same order as `table` at plan creation).  Elements whose cut rule is
+ * empty for (dt) contribute nothing (the reference's `ir == nullptr` return, xfem/symboliccutbfi.cpp:119-120).
+ * accumulate == 0: rows of the plan are overwritten; != 0: added to.  err as in ngsx_classify (may be NULL). */
+int ngsx_assemble_csr_rows_h1(const ngsx_mesh *mesh, const double *lset_v, int fe_order, int dt, int intorder,
+                              const ngsx_form_h1 *h_form, int64_t nlist, const int32_t *els, ngsx_rowplan *plan,
+                              int accumulate, double *vals, int64_t *err, void *stream);
+
 /* ---- Integrate ------------------------------------------------------------------------------------------------- */
 /* out[0] = sum_e sum_q |det J_e| w_q f(x_q) over the (dt, order) cut rule; fixed-shape tree reduction (bitwise
  * reproducible run to run).  out is a device double. */

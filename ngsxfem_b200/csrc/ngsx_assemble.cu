@@ -17,6 +17,7 @@
 #include <cstring>
 #include <vector>
 #include "ngsx_host.cuh"
+#include "ngsx_rows.cuh"
 
 namespace ngsx {
 
@@ -34,6 +35,8 @@ struct ElmatArgs {
   const double4 *rule_if;  int nr_if;
   FormDev form;
   const int32_t *els;          // list of element numbers (NULL: identity)
+  const int32_t *sublist;      // optional indirection: work item k -> list index sublist[k] (output stays at k)
+  const int32_t *d_count;      // optional device-resident number of work items (overrides `count`)
   int group;                   // list entries per warp-sequential group
   int use_fast;                // constant-rule path for uncut elements
   // sinks
@@ -151,13 +154,15 @@ __global__ void __launch_bounds__(WARPS * 32) k_elmat(ElmatArgs A, int64_t first
     ej[t] = idx < NE ? idx % ND : 0;
   }
 
+  if (A.d_count) count = *A.d_count;
   const int64_t ngroups = (count + A.group - 1) / A.group;
   const int64_t nwarps = (int64_t)gridDim.x * WARPS;
   for (int64_t g = (int64_t)blockIdx.x * WARPS + warp; g < ngroups; g += nwarps) {
     const int64_t kb = first + g * A.group;
     const int64_t ke = min(kb + (int64_t)A.group, first + count);
     for (int64_t k = kb; k < ke; k++) {
-      const int64_t e = A.els ? A.els[k] : k;
+      const int64_t kk = A.sublist ? A.sublist[k] : k;
+      const int64_t e = A.els ? A.els[kk] : kk;
       double ls[4], p[DIM + 1][DIM];
       load_el<DIM>(A.M, A.lset, e, ls, p);
       int mask;
@@ -532,6 +537,112 @@ static int dispatch_elvec(const ElvecArgs &A, int fe_order, int sm_count, int nc
   return NGSX_ERR_UNSUPPORTED;
 }
 
+// ---------------------------------------------------------------------------------------------------------------
+// feeders of the owner-computes row gather (ngsx_rows.cu)
+// ---------------------------------------------------------------------------------------------------------------
+// reference tables of the constant-rule path: tab[q][i][j] = sum_r w_r (d_a phi_i d_b phi_j [+ d_b phi_i d_a phi_j]) for the
+// q-th pair a <= b, tab[NPAIR][i][j] = sum_r w_r phi_i phi_j, over the reference rule of the requested order
+template <int DIM, int ORDER>
+__global__ void __launch_bounds__(128) k_ref_tables(const double4 *__restrict__ rule, int nr, double *__restrict__ tab) {
+  constexpr int ND = H1<DIM, ORDER>::ND, NE = ND * ND, NPAIR = DIM * (DIM + 1) / 2;
+  double glr[DIM + 1][DIM];
+#pragma unroll
+  for (int k = 0; k <= DIM; k++)
+#pragma unroll
+    for (int d = 0; d < DIM; d++) glr[k][d] = (k == DIM) ? -1.0 : (k == d ? 1.0 : 0.0);
+  for (int idx = threadIdx.x; idx < NE; idx += blockDim.x) {
+    int i = idx / ND, j = idx % ND;
+    double acc[NPAIR + 1];
+#pragma unroll
+    for (int k = 0; k <= NPAIR; k++) acc[k] = 0.0;
+    for (int q = 0; q < nr; q++) {
+      double4 r = rule[q];
+      double lam[4] = {r.x, r.y, r.z, 0.0};
+      double last = 1.0;
+#pragma unroll
+      for (int k = 0; k < DIM; k++) last -= lam[k];
+      lam[DIM] = last;
+      double si, sj, gi[DIM], gj[DIM];
+      h1_shape_grad<DIM, ORDER>(i, lam, glr, si, gi);
+      h1_shape_grad<DIM, ORDER>(j, lam, glr, sj, gj);
+      int pr = 0;
+#pragma unroll
+      for (int a = 0; a < DIM; a++)
+#pragma unroll
+        for (int b = a; b < DIM; b++) {
+          acc[pr] += r.w * (a == b ? gi[a] * gj[a] : (gi[a] * gj[b] + gi[b] * gj[a]));
+          pr++;
+        }
+      acc[NPAIR] += r.w * si * sj;
+    }
+#pragma unroll
+    for (int k = 0; k <= NPAIR; k++) tab[k * NE + idx] = acc[k];
+  }
+}
+
+// one thread per list entry: sign test, then either the 7 geometry factors of the constant-rule path or a slot in the
+// quadrature work list.  The slot order depends on the atomic counter, the values do not.
+template <int DIM>
+__global__ void __launch_bounds__(256) k_geom(ngsx_mesh M, const double *__restrict__ lset, const int32_t *__restrict__ els, int64_t nlist,
+                                             int dt, FormDev form, int use_fast, double *__restrict__ G, int32_t *__restrict__ cutlist,
+                                             int32_t *__restrict__ cutcount, unsigned long long *__restrict__ err) {
+  constexpr int NPAIR = DIM * (DIM + 1) / 2;
+  int64_t k = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (k >= nlist) return;
+  const int64_t e = els ? els[k] : k;
+  double ls[4], p[DIM + 1][DIM];
+  load_el<DIM>(M, lset, e, ls, p);
+  int mask;
+  const int dom = sign_test<DIM>(ls, mask);
+  double g[GSTRIDE];
+#pragma unroll
+  for (int q = 0; q < GSTRIDE; q++) g[q] = 0.0;
+  long long code = -1;
+  if (dom == -1) {
+    if (err) {
+      atomicAdd(&err[0], 1ULL);
+      atomicMin(reinterpret_cast<long long *>(&err[1]), (long long)e);
+    }
+  } else if (dom == IF || dom == dt) {
+    if (dom != IF && use_fast) {
+      ElGeom<DIM> Gm;
+      element_geometry<DIM>(p, Gm);
+      const double meas = fabs(Gm.det);
+      double cm = form.cm, cs = form.cs;
+      if (form.pm | form.ps) {
+        double h = DIM == 2 ? sqrt(meas) : cbrt(meas);
+        cm *= ipow(h, form.pm); cs *= ipow(h, form.ps);
+      }
+      int pr = 0;
+#pragma unroll
+      for (int a = 0; a < DIM; a++)
+#pragma unroll
+        for (int b = a; b < DIM; b++) {
+          double s = 0.0;
+#pragma unroll
+          for (int d = 0; d < DIM; d++) s += Gm.Jinv[a][d] * Gm.Jinv[b][d];
+          g[pr++] = meas * cs * s;
+        }
+      static_assert(NPAIR <= 6, "geometry record too small");
+      g[6] = meas * cm;
+      code = 0;
+    } else {
+      int slot = atomicAdd(cutcount, 1);
+      cutlist[slot] = (int32_t)k;
+      code = (long long)slot + 1;
+    }
+  }
+  g[7] = __longlong_as_double(code);
+  double4 *out = reinterpret_cast<double4 *>(G + k * GSTRIDE);
+  out[0] = make_double4(g[0], g[1], g[2], g[3]);
+  out[1] = make_double4(g[4], g[5], g[6], g[7]);
+}
+
+template <int DIM, int ORDER>
+static void launch_ref_tables(const double4 *rule, int nr, double *tab, cudaStream_t st) {
+  k_ref_tables<DIM, ORDER><<<1, 128, 0, st>>>(rule, nr, tab);
+}
+
 static int g_use_fast = 1;
 
 }  // namespace ngsx
@@ -578,6 +689,51 @@ int ngsx_assemble_csr_h1(const ngsx_mesh *mesh, const double *lset_v, int fe_ord
   A.els = els; A.group = group; A.use_fast = g_use_fast && h_form->c_nitsche == 0.0;
   A.slots = slots; A.vals = vals;
   return dispatch_elmat<1>(A, fe_order, dd->sm_count, ncolors, h_color_ptr, nlist, as_stream(stream));
+}
+
+int ngsx_assemble_csr_rows_h1(const ngsx_mesh *mesh, const double *lset_v, int fe_order, int dt, int intorder,
+                              const ngsx_form_h1 *h_form, int64_t nlist, const int32_t *els, ngsx_rowplan *plan,
+                              int accumulate, double *vals, int64_t *err, void *stream) {
+  const DeviceData *dd; const double4 *rv, *ri; int nv, ni;
+  NGSX_REQUIRE(h_form && plan && nlist >= 0 && nlist == plan->nlist, "assemble_csr_rows_h1: bad arguments (nlist must match the plan)");
+  NGSX_REQUIRE(plan->nrows == 0 || vals, "assemble_csr_rows_h1: vals is NULL");
+  if (int rc = fill_common(mesh, lset_v, fe_order, dt, intorder, &dd, &rv, &nv, &ri, &ni)) return rc;
+  const int dim = mesh->dim, npairtab = dim * (dim + 1) / 2;
+  const int nd = dim == 2 ? (fe_order == 1 ? 3 : 6) : (fe_order == 1 ? 4 : 10);
+  NGSX_REQUIRE(nd == plan->nd, "assemble_csr_rows_h1: the plan was built for another element type");
+  cudaStream_t st = as_stream(stream);
+  if (err) {
+    int64_t init[2] = {0, INT64_MAX};
+    NGSX_CUDA(cudaMemcpyAsync(err, init, sizeof init, cudaMemcpyHostToDevice, st));
+  }
+  if (nlist == 0 || plan->nrows == 0) return NGSX_OK;
+  if (int rc = rows_scratch(plan, npairtab)) return rc;
+  FormDev form;
+  fill_form(h_form, form);
+  const int use_fast = g_use_fast && h_form->c_nitsche == 0.0 && dt != IF;
+  // 1. reference tables (tiny), 2. geometry factors + quadrature work list, 3. cut-element matrices, 4. row gather
+  switch (dim * 10 + fe_order) {
+    case 21: launch_ref_tables<2, 1>(rv, nv, plan->tab, st); break;
+    case 22: launch_ref_tables<2, 2>(rv, nv, plan->tab, st); break;
+    case 31: launch_ref_tables<3, 1>(rv, nv, plan->tab, st); break;
+    case 32: launch_ref_tables<3, 2>(rv, nv, plan->tab, st); break;
+  }
+  NGSX_LAUNCH_CHECK();
+  NGSX_CUDA(cudaMemsetAsync(plan->cutcount, 0, sizeof(int32_t), st));
+  auto *e = reinterpret_cast<unsigned long long *>(err);
+  const unsigned nb = (unsigned)((nlist + 255) / 256);
+  if (dim == 2) k_geom<2><<<nb, 256, 0, st>>>(*mesh, lset_v, els, nlist, dt, form, use_fast, plan->G, plan->cutlist, plan->cutcount, e);
+  else k_geom<3><<<nb, 256, 0, st>>>(*mesh, lset_v, els, nlist, dt, form, use_fast, plan->G, plan->cutlist, plan->cutcount, e);
+  NGSX_LAUNCH_CHECK();
+  ElmatArgs A{};
+  A.M = *mesh; A.lset = lset_v; A.tab = dd->cut_table; A.dt = dt;
+  A.rule_vol = rv; A.nr_vol = nv; A.rule_if = ri; A.nr_if = ni;
+  A.form = form;
+  A.els = els; A.sublist = plan->cutlist; A.d_count = plan->cutcount; A.group = 1; A.use_fast = 0;
+  A.elmats = plan->cutmats; A.npts = nullptr;
+  // the work-list length lives on the device: launch the persistent grid for the worst case, idle CTAs leave at once
+  if (int rc = dispatch_elmat<0>(A, fe_order, dd->sm_count, 1, nullptr, nlist, st)) return rc;
+  return launch_rows(plan, npairtab, accumulate, vals, dd->sm_count, st);
 }
 
 static int fill_poly(const ngsx_poly *f, PolyDev2 &d) {

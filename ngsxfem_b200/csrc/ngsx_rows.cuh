@@ -1,0 +1,34 @@
+// ngsx_rows.cuh -- the owner-computes ("row gather") assembly plan shared by ngsx_rows.cu (plan construction, row kernel)
+// and ngsx_assemble.cu (geometry-factor / cut-element passes that feed it).
+#pragma once
+#include "ngsx_host.cuh"
+
+// One (row, element) pair descriptor, DS = roundup(5 + nd, 4) bytes:
+//   int32 k        list index of the element
+//   uint8 i        local row (the dof of the row inside element k)
+//   uint8 pos[nd]  position of local column j inside the CSR row
+struct ngsx_rowplan {
+  int64_t nlist = 0, ndof = 0, npairs = 0, nrows = 0, nnz_covered = 0, max_row = 0, nnz_lo = 0, nnz_hi = 0;
+  int32_t nd = 0, ds = 0;
+  int32_t *rows = nullptr;          // [nrows] dof number of the non-empty rows, ascending
+  int64_t *pairptr = nullptr;       // [nrows + 1]
+  uint8_t *desc = nullptr;          // [npairs][ds]
+  const int64_t *rowptr = nullptr;  // caller-owned CSR (must outlive the plan)
+  // scratch of the numeric phase, allocated on first use
+  double *G = nullptr;              // [nlist][8] geometry factors + code
+  int32_t *cutlist = nullptr;       // [nlist] list indices of the elements that need quadrature
+  int32_t *cutcount = nullptr;      // [1]
+  double *cutmats = nullptr;        // [nlist][nd*nd]
+  double *tab = nullptr;            // [(npair+1)][nd*nd] reference tables of the constant-rule path
+};
+
+namespace ngsx {
+
+// geometry-factor record (8 doubles per list entry): g[0..5] = |det J| c_stiff (J^-1 J^-T) upper triangle, g[6] = |det J| c_mass,
+// g[7] = code as int64: -1 no contribution, 0 constant-rule element, s+1 = row s of cutmats
+constexpr int GSTRIDE = 8;
+
+int rows_scratch(ngsx_rowplan *plan, int npairtab);
+int launch_rows(const ngsx_rowplan *plan, int npairtab, int accumulate, double *vals, int sm_count, cudaStream_t st);
+
+}  // namespace ngsx

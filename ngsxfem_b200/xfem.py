@@ -335,6 +335,23 @@ class _Plan:
         self.h_color_ptr = (ctypes.c_int64 * len(color_ptr))(*color_ptr)
 
 
+class _RowPlan:
+    """owner-computes plan of one integrator (ngsx_rowplan): element list + per-row gather descriptors on the device"""
+    ncolors = 0
+
+    def __init__(self, els, table, handle, info):
+        self.els, self.table, self.handle = els, table, handle
+        self.nrows, self.npairs, self.nnz_covered, self.max_row, self.nnz_lo, self.nnz_hi = info
+
+    def __del__(self):
+        try:
+            if self.handle is not None:
+                _lib_().ngsx_rowplan_destroy(self.handle)
+                self.handle = None
+        except Exception:
+            pass
+
+
 def color_list(table: torch.Tensor, ndof: int, group: int):
     """ngsx_color_groups on the host copy of a dof table [n][nd]; returns (perm (device), color_ptr list)"""
     n, nd = table.shape
@@ -351,6 +368,7 @@ class BilinearForm:
     """T_BilinearForm<double> stand-in: `a += integrator`, `a.Assemble()`, `a.mat` (CSR on the device).
     The sparsity is the full element (and, with dgjumps, facet-patch) graph like NGSolve's GetGraph."""
     group_size = 6
+    assembly = "rows"          # "rows": owner-computes row gather (default); "colored": colour-ordered scatter-add
 
     def __init__(self, space: H1, symmetric: bool = False, check_unused: bool = False, **_):
         self.space = space
@@ -358,6 +376,9 @@ class BilinearForm:
         self.mat: Optional[CSRMatrix] = None
         self._plans: Dict[int, _Plan] = {}
         self._graph_key = None
+        self._err = torch.zeros((1, 2), dtype=torch.int64, device=space.mesh.device)     # one {count, first} per integrator
+        self._err_armed = False
+        self.row_range = None      # (lo, hi): this rank owns CSR rows [lo, hi) (multi-GPU owner-computes partition)
 
     def __iadd__(self, integ):
         if not isinstance(integ, (SymbolicCutBFI, SymbolicFacetPatchBFI)):
@@ -413,11 +434,42 @@ class BilinearForm:
             ba = ba & integ.definedonelements
         return ba.nonzero()
 
+    def _listed_elements(self, integ: SymbolicCutBFI) -> torch.Tensor:
+        """elements the integrator may ever touch: the graph's elements restricted by definedonelements.  Independent of the
+        current level-set values, so the plan survives a level-set update (the kernel re-classifies every listed element)."""
+        els = self._graph_elements()
+        if integ.definedonelements is not None:
+            de = integ.definedonelements.to_bool()
+            els = torch.nonzero(de).reshape(-1) if els is None else els[de[els]]
+        if els is None:
+            els = torch.arange(self.space.mesh.ne, device=self.space.mesh.device)
+        return els
+
+    def _row_plan(self, integ: SymbolicCutBFI) -> _RowPlan:
+        fes, L = self.space, _lib_()
+        els = self._listed_elements(integ).to(torch.int32).contiguous()
+        table = fes.el2dof[els.long()].contiguous()
+        h = ctypes.c_void_p()
+        lo, hi = self.row_range if self.row_range is not None else (0, fes.ndof)
+        check(L.ngsx_rowplan_create(els.numel(), fes.nd, _ptr(table), fes.ndof, _ptr(self.mat.rowptr), _ptr(self.mat.colidx),
+                                    lo, hi, ctypes.byref(h), _stream()))
+        info = (ctypes.c_int64 * 6)()
+        check(L.ngsx_rowplan_info(h, info))
+        return _RowPlan(els, table, h, tuple(info))
+
     def _plan_for(self, k: int, integ) -> _Plan:
         if k in self._plans:
             return self._plans[k]
         fes, L = self.space, _lib_()
-        if isinstance(integ, SymbolicCutBFI):
+        if isinstance(integ, SymbolicCutBFI) and self.assembly == "rows":
+            try:
+                plan = self._row_plan(integ)
+            except NgsxError as exc:
+                if exc.status != -2:
+                    raise
+                self.assembly = "colored"              # a CSR row longer than 256 entries: coloured scatter instead
+                return self._plan_for(k, integ)
+        elif isinstance(integ, SymbolicCutBFI):
             els = self._active_elements(integ)
             table = fes.el2dof[els].contiguous()
             perm, cptr = color_list(table, fes.ndof, self.group_size)
@@ -465,11 +517,23 @@ class BilinearForm:
         if self.mat is None or reallocate:
             self._build_graph()
             self._plans.clear()
-        self.mat.vals.zero_()
+        plans = [self._plan_for(k, integ) for k, integ in enumerate(self.integrators)]
+        # a single row plan that covers every stored entry overwrites its rows: no SetZero pass, each value written once
+        overwrite = len(plans) == 1 and isinstance(plans[0], _RowPlan) and plans[0].nnz_covered == self.mat.nnz
+        if not overwrite:
+            self.mat.vals.zero_()
+        if self._err.shape[0] < len(plans):
+            self._err = torch.zeros((len(plans), 2), dtype=torch.int64, device=fes.mesh.device)
         mesh_c = ctypes.byref(fes.mesh.c_struct())
         for k, integ in enumerate(self.integrators):
-            plan = self._plan_for(k, integ)
-            if isinstance(integ, SymbolicCutBFI):
+            plan = plans[k]
+            if isinstance(plan, _RowPlan):
+                lv = _lset_vec(integ.lset)
+                check(L.ngsx_assemble_csr_rows_h1(mesh_c, _ptr(lv), fes.order, integ.dt, integ.intorder(fes.order), ctypes.byref(integ.form),
+                                                  plan.els.numel(), _ptr(plan.els), plan.handle, 0 if overwrite else 1,
+                                                  _ptr(self.mat.vals), _ptr(self._err[k]), _stream()))
+                self._err_armed = True
+            elif isinstance(integ, SymbolicCutBFI):
                 lv = _lset_vec(integ.lset)
                 check(L.ngsx_assemble_csr_h1(mesh_c, _ptr(lv), fes.order, integ.dt, integ.intorder(fes.order), ctypes.byref(integ.form),
                                              plan.els.numel(), _ptr(plan.els), _ptr(plan.slots), plan.ncolors, plan.h_color_ptr,
@@ -477,6 +541,17 @@ class BilinearForm:
             else:
                 self._assemble_facetpatch(integ, plan)
         return self
+
+    def check_degenerate(self):
+        """raise if the last Assemble met a level set the reference throws on; synchronises"""
+        if not self._err_armed:
+            return
+        self._err_armed = False
+        err = self._err.tolist()
+        n, first = sum(r[0] for r in err), min(r[1] for r in err)
+        if n:
+            raise NgsxError(-4, f"{n} element(s) carry a level set the reference rejects (first: element {first}): "
+                                "'You tried to cut a simplex with a plain geometry lset function'")
 
     def _assemble_facetpatch(self, integ, plan):
         """patch matrices on the device (ngsx_facetpatch_elmat_h1), duplicate dofs merged like NGSolve's compressed_elmat,

@@ -183,8 +183,8 @@ def test_small_mesh_against_reference_golden(X, golden_meshes, tag):
 @pytest.mark.parametrize("dim,nx", [(2, 24), (3, 9)])
 @pytest.mark.parametrize("fo", [1, 2])
 @pytest.mark.parametrize("dt", [NEG, POS, IF])
-@pytest.mark.parametrize("group", [1, 6])
-def test_assemble_csr_against_oracle(X, dim, nx, fo, dt, group):
+@pytest.mark.parametrize("mode,group", [("rows", 1), ("colored", 1), ("colored", 6)])
+def test_assemble_csr_against_oracle(X, dim, nx, fo, dt, mode, group):
     from oracle import orc
     m = X.meshes.MakeStructured2DMesh(nx) if dim == 2 else X.meshes.MakeStructured3DMesh(nx)
     mesh = X.ngs.Mesh(m)
@@ -196,17 +196,21 @@ def test_assemble_csr_against_oracle(X, dim, nx, fo, dt, group):
     Vh = X.ngs.H1(mesh, order=fo)
     u, v = Vh.TnT()
     a = X.xfem.BilinearForm(Vh)
-    a.group_size = group
+    a.group_size, a.assembly = group, mode
     a += X.xfem.SymbolicBFI(levelset_domain={"levelset": gf, "domain_type": dt}, form=0.7 * X.ngs.grad(u) * X.ngs.grad(v) + 1.3 * u * v)
     a.Assemble()
+    a.check_degenerate()
+    assert a.assembly == mode
     first = a.mat.vals.clone()
+    a.mat.vals.fill_(float("nan"))                                                 # rows mode overwrites, coloured mode zero-fills first
     a.Assemble()                                                                   # bitwise reproducible (no FP atomics)
     assert torch.equal(first, a.mat.vals)
     el2v, vert, ls = mesh.el2v.cpu().numpy(), mesh.vert.cpu().numpy(), gf.vec.cpu().numpy()
     els = np.arange(mesh.ne, dtype=np.int32)
     vals, nass = orc.assemble_csr(dim, el2v, vert, ls, fo, Vh.el2dof.cpu().numpy(), dt, a.integrators[0].intorder(fo), 1.3, 0.7,
                                   np.array([0, mesh.ne]), els, a.mat.rowptr.cpu().numpy(), a.mat.colidx.cpu().numpy(), nthreads=1)
-    assert nass == a._plans[0].els.numel()
+    if mode == "colored":
+        assert nass == a._plans[0].els.numel()
     got = a.mat.vals.cpu().numpy()
     assert np.abs(got - vals).max() <= RTOL * np.abs(vals).max()
     # the sparsity is the full element graph: same pattern as scipy's from the dof table
@@ -406,3 +410,11 @@ def test_full_size_properties(X):
     r = torch.zeros(Vh.ndof, dtype=torch.float64, device="cuda")
     r.index_add_(0, rows, b.mat.vals * ones[b.mat.colidx.long()])
     assert r.abs().max().item() < 1e-9 * b.mat.vals.abs().max().item()
+    # owner-computes row gather vs colour-ordered scatter-add: same operator at full size (different summation order)
+    assert b.assembly == "rows" and b._plans[0].nnz_covered == b.mat.nnz
+    c = X.xfem.RestrictedBilinearForm(Vh, element_restriction=ci.GetElementsOfType(X.xfem.HASNEG))
+    c.assembly = "colored"
+    c += X.xfem.SymbolicBFI(levelset_domain=ld(NEG), form=X.ngs.grad(u) * X.ngs.grad(v))
+    c.Assemble()
+    assert torch.equal(b.mat.colidx, c.mat.colidx)
+    assert (b.mat.vals - c.mat.vals).abs().max().item() <= RTOL * c.mat.vals.abs().max().item()
