@@ -643,6 +643,175 @@ static void launch_ref_tables(const double4 *rule, int nr, double *tab, cudaStre
   k_ref_tables<DIM, ORDER><<<1, 128, 0, st>>>(rule, nr, tab);
 }
 
+// ---------------------------------------------------------------------------------------------------------------
+// quadrature element matrices, ONE THREAD PER ELEMENT (work list of the row gather: cut elements, Nitsche / IF forms).
+// All supported forms are symmetric, so a thread keeps the ND(ND+1)/2 upper-triangle accumulators in registers, walks the
+// sub-simplices and their rule points itself (rule and decomposition table are shared-memory broadcasts) and mirrors the
+// block on store.  No shared-memory staging, no lane idles on the 14-point rules; the dense nd x nd block of work item s
+// goes to elmats[s].
+// ---------------------------------------------------------------------------------------------------------------
+constexpr int CUTMAT_THREADS = 128;
+
+template <int DIM, int ORDER>
+__global__ void __launch_bounds__(CUTMAT_THREADS) k_cutmat(ElmatArgs A, int64_t count) {
+  constexpr int ND = H1<DIM, ORDER>::ND, NE = ND * ND, NS = ND * (ND + 1) / 2, NEDGE = ND - (DIM + 1);
+  extern __shared__ __align__(16) unsigned char smem_raw[];
+  double4 *srule_vol = reinterpret_cast<double4 *>(smem_raw);
+  double4 *srule_if = srule_vol + A.nr_vol;
+  CutEntry *lut = reinterpret_cast<CutEntry *>(srule_if + A.nr_if);
+  for (int i = threadIdx.x; i < A.nr_vol; i += blockDim.x) srule_vol[i] = A.rule_vol[i];
+  for (int i = threadIdx.x; i < A.nr_if; i += blockDim.x) srule_if[i] = A.rule_if[i];
+  if (threadIdx.x < 16) lut[threadIdx.x] = A.tab->e[DIM - 2][A.dt][threadIdx.x];
+  __syncthreads();
+  if (A.d_count) count = *A.d_count;
+  for (int64_t s = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; s < count; s += (int64_t)gridDim.x * blockDim.x) {
+    const int64_t kk = A.sublist ? A.sublist[s] : s;
+    const int64_t e = A.els ? A.els[kk] : kk;
+    double ls[4], p[DIM + 1][DIM];
+    load_el<DIM>(A.M, A.lset, e, ls, p);
+    int mask;
+    const int dom = sign_test<DIM>(ls, mask);
+    const bool cut = dom == IF;
+    double acc[NS];
+#pragma unroll
+    for (int t = 0; t < NS; t++) acc[t] = 0.0;
+    if (cut || dom == A.dt) {
+      ElGeom<DIM> G;
+      element_geometry<DIM>(p, G);
+      const double meas = fabs(G.det);
+      double cm = A.form.cm, cs = A.form.cs, cn = A.form.cn;
+      if (A.form.pm | A.form.ps | A.form.pn) {
+        double h = DIM == 2 ? sqrt(meas) : cbrt(meas);
+        cm *= ipow(h, A.form.pm); cs *= ipow(h, A.form.ps); cn *= ipow(h, A.form.pn);
+      }
+      double gl[DIM + 1][DIM];
+      bary_gradients<DIM>(G, gl);
+      double nrm[DIM], scale = 1.0;
+      {
+        double g2 = 0.0, r2 = 0.0;
+#pragma unroll
+        for (int d = 0; d < DIM; d++) {
+          double v = 0.0;
+#pragma unroll
+          for (int k = 0; k <= DIM; k++) v += ls[k] * gl[k][d];
+          nrm[d] = v; g2 += v * v;
+        }
+#pragma unroll
+        for (int k = 0; k < DIM; k++) { double v = ls[k] - ls[DIM]; r2 += v * v; }
+        const double inv = 1.0 / sqrt(g2);
+#pragma unroll
+        for (int d = 0; d < DIM; d++) nrm[d] *= inv;
+        if (cut && A.dt == IF) scale = sqrt(g2) / sqrt(r2);           // |F^-T n_ref|
+      }
+      // normal derivatives of the barycentrics (Nitsche terms)
+      double gln[DIM + 1];
+#pragma unroll
+      for (int k = 0; k <= DIM; k++) {
+        double v = 0.0;
+#pragma unroll
+        for (int d = 0; d < DIM; d++) v += gl[k][d] * nrm[d];
+        gln[k] = v;
+      }
+      CutEntry E;
+      if (cut) E = lut[mask]; else { E.ns = 1; E.npt = 0; }
+      const double4 *rule = (cut && A.dt == IF) ? srule_if : srule_vol;
+      const int nr = (cut && A.dt == IF) ? A.nr_if : A.nr_vol;
+      for (int sub = 0; sub < E.ns; sub++) {
+        double P[4][3];
+        double sfac = 1.0;
+        if (cut) {
+          for (int v = 0; v < E.npt; v++) coded_point<DIM>(E.v[sub][v], ls, P[v]);
+          sfac = simplex_factor(E.npt, P);
+        }
+        const double f0 = meas * sfac * scale;
+        for (int q = 0; q < nr; q++) {
+          const double4 r = rule[q];
+          double xi[3] = {r.x, r.y, r.z};
+          if (cut) simplex_point(E.npt, P, r, xi);
+          double lam[DIM + 1];
+          double last = 1.0;
+#pragma unroll
+          for (int k = 0; k < DIM; k++) { lam[k] = xi[k]; last -= xi[k]; }
+          lam[DIM] = last;
+          const double f = f0 * r.w;
+          // B rows: value, gradient, normal derivative of every shape function at this point
+          double sv[ND], gv[ND][DIM], gn[ND];
+#pragma unroll
+          for (int i = 0; i <= DIM; i++) {
+            sv[i] = lam[i]; gn[i] = gln[i];
+#pragma unroll
+            for (int d = 0; d < DIM; d++) gv[i][d] = gl[i][d];
+          }
+          if constexpr (ORDER == 2) {
+#pragma unroll
+            for (int ed = 0; ed < NEDGE; ed++) {
+              int a, b;
+              edge_vertices<DIM>(ed, a, b);
+              const int i = DIM + 1 + ed;
+              sv[i] = -0.5 * lam[a] * lam[b];
+              gn[i] = -0.5 * (gln[a] * lam[b] + lam[a] * gln[b]);
+#pragma unroll
+              for (int d = 0; d < DIM; d++) gv[i][d] = -0.5 * (gl[a][d] * lam[b] + lam[a] * gl[b][d]);
+            }
+          }
+          const double fs = f * cs, fm = f * cm, fn = f * cn;
+          int t = 0;
+#pragma unroll
+          for (int i = 0; i < ND; i++) {
+            double ag[DIM];
+#pragma unroll
+            for (int d = 0; d < DIM; d++) ag[d] = fs * gv[i][d];
+            const double am = fm * sv[i] + fn * gn[i], an = fn * sv[i];     // (cm phi_i + cn dn phi_i) phi_j + cn phi_i dn phi_j
+#pragma unroll
+            for (int j = 0; j <= i; j++) {
+              double v = am * sv[j];
+#pragma unroll
+              for (int d = 0; d < DIM; d++) v += ag[d] * gv[j][d];
+              if (cn != 0.0) v += an * gn[j];
+              acc[t++] += v;
+            }
+          }
+        }
+      }
+    }
+    double *out = A.elmats + s * NE;
+    int t = 0;
+#pragma unroll
+    for (int i = 0; i < ND; i++)
+#pragma unroll
+      for (int j = 0; j <= i; j++) {
+        out[i * ND + j] = acc[t];
+        if (j != i) out[j * ND + i] = acc[t];
+        t++;
+      }
+  }
+}
+
+template <int DIM, int ORDER>
+static int launch_cutmat_t(const ElmatArgs &A, int sm_count, int64_t maxcount, cudaStream_t st) {
+  size_t smem = (size_t)(A.nr_vol + A.nr_if) * sizeof(double4) + 16 * sizeof(CutEntry);
+  auto kern = k_cutmat<DIM, ORDER>;
+  int occ = 0;
+  NGSX_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, kern, CUTMAT_THREADS, smem));
+  if (occ < 1) { set_error("cut-element kernel does not fit on an SM"); return NGSX_ERR_CUDA; }
+  int64_t need = (maxcount + CUTMAT_THREADS - 1) / CUTMAT_THREADS;
+  unsigned grid = (unsigned)std::max<int64_t>(1, std::min<int64_t>(need, (int64_t)sm_count * occ));
+  kern<<<grid, CUTMAT_THREADS, smem, st>>>(A, maxcount);
+  NGSX_LAUNCH_CHECK();
+  return NGSX_OK;
+}
+
+static int launch_cutmat(const ElmatArgs &A, int fe_order, int sm_count, int64_t maxcount, cudaStream_t st) {
+  switch (A.M.dim * 10 + fe_order) {
+    case 21: return launch_cutmat_t<2, 1>(A, sm_count, maxcount, st);
+    case 22: return launch_cutmat_t<2, 2>(A, sm_count, maxcount, st);
+    case 31: return launch_cutmat_t<3, 1>(A, sm_count, maxcount, st);
+    case 32: return launch_cutmat_t<3, 2>(A, sm_count, maxcount, st);
+  }
+  set_error("unsupported (dim, order)");
+  return NGSX_ERR_UNSUPPORTED;
+}
+
 static int g_use_fast = 1;
 
 }  // namespace ngsx
@@ -732,7 +901,7 @@ int ngsx_assemble_csr_rows_h1(const ngsx_mesh *mesh, const double *lset_v, int f
   A.els = els; A.sublist = plan->cutlist; A.d_count = plan->cutcount; A.group = 1; A.use_fast = 0;
   A.elmats = plan->cutmats; A.npts = nullptr;
   // the work-list length lives on the device: launch the persistent grid for the worst case, idle CTAs leave at once
-  if (int rc = dispatch_elmat<0>(A, fe_order, dd->sm_count, 1, nullptr, nlist, st)) return rc;
+  if (int rc = launch_cutmat(A, fe_order, dd->sm_count, nlist, st)) return rc;
   return launch_rows(plan, npairtab, accumulate, vals, dd->sm_count, st);
 }
 

@@ -3,16 +3,22 @@
 #pragma once
 #include "ngsx_host.cuh"
 
-// One (row, element) pair descriptor, DS = roundup(5 + nd, 4) bytes:
+// One (row, element) pair descriptor, 16 bytes (one LDG.128):
 //   int32 k        list index of the element
 //   uint8 i        local row (the dof of the row inside element k)
-//   uint8 pos[nd]  position of local column j inside the CSR row
+//   uint8 pos[nd]  position of local column j inside the CSR row (nd <= 11)
+namespace ngsx {
+struct RowRec { uint32_t p0; uint16_t np; uint16_t off; };   // first pair, number of pairs, offset of the row inside its chunk
+}
 struct ngsx_rowplan {
   int64_t nlist = 0, ndof = 0, npairs = 0, nrows = 0, nnz_covered = 0, max_row = 0, nnz_lo = 0, nnz_hi = 0;
   int32_t nd = 0, ds = 0;
   int32_t *rows = nullptr;          // [nrows] dof number of the non-empty rows, ascending
   int64_t *pairptr = nullptr;       // [nrows + 1]
   uint8_t *desc = nullptr;          // [npairs][ds]
+  ngsx::RowRec *rowrec = nullptr;   // [nrows]
+  int32_t *chunk_q = nullptr;       // [nchunks + 1] first plan row of each chunk
+  int64_t nchunks = 0;
   const int64_t *rowptr = nullptr;  // caller-owned CSR (must outlive the plan)
   // scratch of the numeric phase, allocated on first use
   double *G = nullptr;              // [nlist][8] geometry factors + code
