@@ -2,6 +2,7 @@
 // Hand-written CUDA for sm_100a; HBM-bound integer/FP64 streaming kernels (one thread per element, warp ballots
 // for bit arrays, one warp per cut simplex for rule emission).
 #include <cub/cub.cuh>
+#include <algorithm>
 #include <cstring>
 #include <mutex>
 #include <vector>
@@ -366,58 +367,98 @@ __device__ __forceinline__ void map_point(const double (*p)[DIM], const double *
   }
 }
 
-// Integrate: one thread per element, fixed-shape block tree -> one partial per block
+// Integrate: one thread per element for the sign test and the uncut elements; every cut element is then handled by the
+// whole warp (lanes = (sub-simplex, rule point) items), so the few long cut elements do not serialise a warp.  All partial
+// sums have a fixed shape (item -> lane assignment, xor-shuffle tree, block tree, final tree): bitwise reproducible.
 template <int DIM>
 __global__ void __launch_bounds__(256) k_integrate(ngsx_mesh M, const double *__restrict__ lset, const CutTable *__restrict__ tab, int dt,
                                                   const double4 *__restrict__ rule_vol, int nr_vol, const double4 *__restrict__ rule_if, int nr_if,
-                                                  PolyDev f, double *__restrict__ partial) {
+                                                  PolyDev f, int fconst, double *__restrict__ partial) {
   extern __shared__ double4 srule[];               // nr_vol + nr_if
   __shared__ CutEntry lut[16];
   __shared__ double wsum[8];
+  __shared__ double wref;                          // sum of the reference weights (constant integrands)
   for (int i = threadIdx.x; i < nr_vol; i += blockDim.x) srule[i] = rule_vol[i];
   for (int i = threadIdx.x; i < nr_if; i += blockDim.x) srule[nr_vol + i] = rule_if[i];
   if (threadIdx.x < 16) lut[threadIdx.x] = tab->e[DIM - 2][dt][threadIdx.x];
   __syncthreads();
-  int64_t e = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (threadIdx.x == 0) {
+    double w = 0.0;
+    for (int q = 0; q < nr_vol; q++) w += srule[q].w;
+    wref = w;
+  }
+  __syncthreads();
+  const unsigned full = 0xffffffffu;
+  const int lane = threadIdx.x & 31;
   double sum = 0.0;
+  // fixed grid, block-stride over tiles of blockDim elements: the shape of the reduction does not depend on the device
+  for (int64_t base = (int64_t)blockIdx.x * blockDim.x; base < M.ne; base += (int64_t)gridDim.x * blockDim.x) {
+  const int64_t e = base + threadIdx.x;
+  int dom = -2;
   if (e < M.ne) {
     int v[4], mask;
-    double ls[4], p[DIM + 1][DIM];
-    load_element<DIM>(M, lset, e, v, ls, p);
-    int dom = sign_test<DIM>(ls, mask);
-    if (dom == IF || dom == dt) {
+    double ls[4];
+    load_element<DIM>(M, lset, e, v, ls, (double(*)[DIM]) nullptr);
+    dom = sign_test<DIM>(ls, mask);
+    if (dom == dt && dom != IF) {                  // uncut element inside the domain: the static reference rule
+      double p[DIM + 1][DIM];
+#pragma unroll
+      for (int k = 0; k <= DIM; k++)
+#pragma unroll
+        for (int d = 0; d < DIM; d++) p[k][d] = __ldg(M.vert + (int64_t)v[k] * DIM + d);
       ElGeom<DIM> G;
       element_geometry<DIM>(p, G);
-      double meas = fabs(G.det);
-      if (dom != IF) {
+      const double meas = fabs(G.det);
+      if (fconst) {
+        sum += meas * (wref * f.c[0]);
+      } else {
         for (int q = 0; q < nr_vol; q++) {
           double4 r = srule[q];
           double xi[3] = {r.x, r.y, r.z}, x[3];
           map_point<DIM>(p, xi, x);
           sum += meas * r.w * eval_poly(f, x);
         }
-      } else {
-        const CutEntry E = lut[mask];
-        const double4 *rule = dt == IF ? srule + nr_vol : srule;
-        int nr = dt == IF ? nr_if : nr_vol;
-        double scale = dt == IF ? interface_scale<DIM>(G, ls) : 1.0;
-        for (int s = 0; s < E.ns; s++) {
-          double P[4][3];
-          for (int k = 0; k < E.npt; k++) coded_point<DIM>(E.v[s][k], ls, P[k]);
-          double fac = simplex_factor(E.npt, P) * scale;
-          for (int q = 0; q < nr; q++) {
-            double xi[3], x[3];
-            simplex_point(E.npt, P, rule[q], xi);
-            map_point<DIM>(p, xi, x);
-            sum += meas * (rule[q].w * fac) * eval_poly(f, x);
-          }
-        }
       }
     }
   }
+  // cut elements, one after the other, by the whole warp
+  unsigned todo = __ballot_sync(full, dom == IF);
+  while (todo) {
+    const int src = __ffs(todo) - 1;
+    todo &= todo - 1;
+    const int64_t ee = e - lane + src;             // element of lane `src`
+    int v[4], mask;
+    double ls[4], p[DIM + 1][DIM];
+    load_element<DIM>(M, lset, ee, v, ls, p);      // same address in every lane: one broadcast transaction
+    sign_test<DIM>(ls, mask);
+    ElGeom<DIM> G;
+    element_geometry<DIM>(p, G);
+    const double meas = fabs(G.det);
+    const CutEntry E = lut[mask];
+    const double4 *rule = dt == IF ? srule + nr_vol : srule;
+    const int nr = dt == IF ? nr_if : nr_vol;
+    const double scale = dt == IF ? interface_scale<DIM>(G, ls) : 1.0;
+    const int nitems = E.ns * nr;
+    double part = 0.0;
+    for (int it = lane; it < nitems; it += 32) {
+      const int s = it / nr, q = it - s * nr;
+      double P[4][3];
+      for (int k = 0; k < E.npt; k++) coded_point<DIM>(E.v[s][k], ls, P[k]);
+      const double fac = simplex_factor(E.npt, P) * scale;
+      double xi[3], x[3];
+      const double4 r = rule[q];
+      simplex_point(E.npt, P, r, xi);
+      map_point<DIM>(p, xi, x);
+      part += meas * (r.w * fac) * (fconst ? f.c[0] : eval_poly(f, x));
+    }
 #pragma unroll
-  for (int o = 16; o > 0; o >>= 1) sum += __shfl_xor_sync(0xffffffffu, sum, o);
-  if ((threadIdx.x & 31) == 0) wsum[threadIdx.x >> 5] = sum;
+    for (int o = 16; o > 0; o >>= 1) part += __shfl_xor_sync(full, part, o);
+    if (lane == src) sum += part;
+  }
+  }
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) sum += __shfl_xor_sync(full, sum, o);
+  if (lane == 0) wsum[threadIdx.x >> 5] = sum;
   __syncthreads();
   if (threadIdx.x == 0) {
     double s = 0.0;
@@ -628,12 +669,13 @@ int ngsx_integrate(const ngsx_mesh *mesh, const double *lset_v, int dt, int orde
   PolyDev f;
   f.n = h_f->nterms;
   for (int m = 0; m < f.n; m++) { f.c[m] = h_f->coef[m]; for (int d = 0; d < 3; d++) f.ex[m][d] = h_f->ex[m][d]; }
-  unsigned nb = nblocks(mesh->ne, 256);
+  unsigned nb = std::min(nblocks(mesh->ne, 256), 2368u);     // fixed upper bound (16 x 148): device-independent reduction shape
   double *partial = nullptr;
   NGSX_CUDA(cudaMallocAsync(&partial, nb * sizeof(double), st));
   size_t smem = (size_t)(nv + ni) * sizeof(double4);
-  if (mesh->dim == 2) k_integrate<2><<<nb, 256, smem, st>>>(*mesh, lset_v, dd->cut_table, dt, rv, nv, ri, ni, f, partial);
-  else k_integrate<3><<<nb, 256, smem, st>>>(*mesh, lset_v, dd->cut_table, dt, rv, nv, ri, ni, f, partial);
+  const int fconst = f.n == 1 && f.ex[0][0] == 0 && f.ex[0][1] == 0 && f.ex[0][2] == 0;
+  if (mesh->dim == 2) k_integrate<2><<<nb, 256, smem, st>>>(*mesh, lset_v, dd->cut_table, dt, rv, nv, ri, ni, f, fconst, partial);
+  else k_integrate<3><<<nb, 256, smem, st>>>(*mesh, lset_v, dd->cut_table, dt, rv, nv, ri, ni, f, fconst, partial);
   g_launches.fetch_add(1);
   cudaError_t e1 = cudaGetLastError();
   k_reduce_final<<<1, 1024, 0, st>>>(nb, partial, out);

@@ -8,8 +8,8 @@
 // (56 B, L2-resident) contracted with per-CTA reference tables; cut elements read their row of a compact element-matrix
 // buffer produced by the quadrature kernel.  No colouring, no zero-fill, no read-modify-write, no floating-point atomics.
 //
-// Work decomposition of the row kernel: CTA = chunk of consecutive rows (values in shared memory), lane group of nd lanes =
-// one row at a time, lane j = column j of the pair's element matrix (see k_rows).
+// Work decomposition of the row kernel: CTA = chunk of consecutive rows (values in shared memory), one thread per
+// contiguous range of rows (see k_rows).
 // HBM traffic per P2 tet pair: 16 B descriptor + (L2) 64 B factors; per CSR entry: 8 B written once.
 #include <cub/cub.cuh>
 #include <thrust/iterator/counting_iterator.h>
@@ -17,10 +17,10 @@
 
 namespace ngsx {
 
-constexpr int RWARPS = 8;
+constexpr int RT = 256;           // threads per CTA of the row kernel
 constexpr int MAXROW = 256;       // longest supported CSR row (column positions are bytes)
-constexpr int CHW = 2816;         // chunk window in CSR entries: a chunk holds the rows that START inside one window
-constexpr int ACC = CHW + MAXROW; // shared-memory accumulator of a chunk (24 KB)
+constexpr int CHW = 7936;         // chunk window in CSR entries: a chunk holds the rows that START inside one window
+constexpr int ACC = CHW + MAXROW; // shared-memory accumulator of a chunk (64 KB)
 
 // ---- plan construction --------------------------------------------------------------------------------------------
 __global__ void __launch_bounds__(256) k_pair_keys(int64_t npairs, const int32_t *__restrict__ table, int64_t row_lo, int64_t row_hi,
@@ -104,6 +104,40 @@ __global__ void __launch_bounds__(256) k_plan_chunks(int64_t nchunks, int64_t nr
   chunk_q[c] = (int32_t)lo;
 }
 
+// thread t of the CTA that owns chunk c walks rows [split[t], split[t+1]): the chunk's pairs are cut into RT equal parts
+// and every cut is moved to the next row boundary
+__global__ void __launch_bounds__(256) k_chunk_split(int64_t nchunks, const int32_t *__restrict__ chunk_q, const int64_t *__restrict__ pairptr,
+                                                    int32_t *__restrict__ split) {
+  int64_t t = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (t >= nchunks * (RT + 1)) return;
+  const int64_t c = t / (RT + 1);
+  const int k = (int)(t - c * (RT + 1));
+  const int q0 = chunk_q[c], q1 = chunk_q[c + 1];
+  if (k == RT || q0 == q1) { split[t] = k == RT ? q1 : q0; return; }
+  const int64_t pa = pairptr[q0], pb = pairptr[q1];
+  const int64_t target = pa + ((pb - pa) * k) / RT;
+  int lo = q0, hi = q1;
+  while (lo < hi) {
+    int mid = (lo + hi) >> 1;
+    if (pairptr[mid] < target) lo = mid + 1; else hi = mid;
+  }
+  split[t] = lo;
+}
+
+// processing order of the chunks: by the list index of the first contributing element, so that the vertex-row and edge-row
+// chunks of one mesh region run at about the same time; empty chunks get the largest key
+__global__ void __launch_bounds__(256) k_chunk_keys(int64_t nchunks, const int32_t *__restrict__ chunk_q, const int64_t *__restrict__ pairptr,
+                                                   const uint8_t *__restrict__ desc, int ds, uint32_t *__restrict__ keys, int32_t *__restrict__ ids,
+                                                   unsigned long long *__restrict__ nonempty) {
+  int64_t c = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (c >= nchunks) return;
+  int q0 = chunk_q[c], q1 = chunk_q[c + 1];
+  ids[c] = (int32_t)c;
+  if (q0 == q1) { keys[c] = 0xffffffffu; return; }
+  keys[c] = (uint32_t)*reinterpret_cast<const int32_t *>(desc + pairptr[q0] * ds);
+  atomicAdd(nonempty, 1ULL);
+}
+
 __global__ void __launch_bounds__(256) k_plan_rowrec(int64_t nrows, int64_t nnz_lo, const int32_t *__restrict__ rows, const int64_t *__restrict__ pairptr,
                                                     const int64_t *__restrict__ rowptr, const int32_t *__restrict__ chunk_q,
                                                     RowRec *__restrict__ rowrec, int *__restrict__ bad) {
@@ -122,13 +156,17 @@ __global__ void __launch_bounds__(256) k_plan_rowrec(int64_t nrows, int64_t nnz_
 // ---- the row kernel ---------------------------------------------------------------------------------------------
 // CTA = one chunk of consecutive CSR rows whose values (<= ACC doubles) live in shared memory: initialised cooperatively
 // (zero, or the current values when accumulating), gathered, and streamed out once with coalesced stores.
-// Inside the chunk every lane group ("slot", nd lanes) owns whole rows: slot s walks rows q0+s, q0+s+NSLOT, ... pair by pair,
-// lane j of the slot computing entry (i, j) of the pair's element matrix and adding it at its position of the row.
-// Slots never share a row, so there is no ordering problem between them; consecutive pairs of one row are ordered by the
-// per-step __syncwarp().  Summation order of every CSR entry = list order of the plan: bitwise reproducible.
+// ONE THREAD PER ROW RANGE: the rows of the chunk are split into RT contiguous ranges, a thread walks the (row, element)
+// pairs of its range in plan order; per pair it contracts the element's 7 geometry factors with row i of the reference
+// tables (nd entries, shared-memory vector loads) and adds them at their positions of the row.  No two threads share a
+// row, so no synchronisation is needed between the cooperative init and the stream-out, and the summation order of every
+// CSR entry is the plan order: bitwise reproducible.  Descriptors are prefetched two pairs ahead, geometry factors one
+// pair ahead, row records one row ahead.
 struct RowArgs {
-  int64_t nchunks;
-  const int32_t *chunk_q;     // [nchunks + 1] first plan row of each chunk
+  int64_t nchunks;            // non-empty chunks
+  const int32_t *chunk_order; // [nchunks] chunk numbers in processing order (mesh locality: geometry factors stay in L2)
+  const int32_t *chunk_q;     // [.. + 1] first plan row of each chunk
+  const int32_t *chunk_split; // [..][RT + 1] first plan row of each thread's range
   const int32_t *rows;
   const RowRec *rowrec;
   const uint4 *desc;
@@ -140,64 +178,129 @@ struct RowArgs {
   int accumulate;
 };
 
+__device__ __forceinline__ RowRec ld_rowrec(const RowRec *p) {
+  const uint2 u = __ldg(reinterpret_cast<const uint2 *>(p));
+  RowRec r;
+  r.p0 = u.x; r.np = (uint16_t)(u.y & 0xffffu); r.off = (uint16_t)(u.y >> 16);
+  return r;
+}
+
+// byte 5 + j of a descriptor = position of local column j in the row
+template <int J> __device__ __forceinline__ int desc_pos(const uint4 &d) {
+  constexpr int b = 5 + J, w = b >> 2, sh = (b & 3) * 8;
+  const uint32_t x = w == 1 ? d.y : (w == 2 ? d.z : d.w);
+  return (int)((x >> sh) & 0xffu);
+}
+
+// positions of the nd local columns (compile-time byte extraction)
+template <int ND, int J> __device__ __forceinline__ void desc_positions(const uint4 &d, int *pos) {
+  if constexpr (J < ND) { pos[J] = desc_pos<J>(d); desc_positions<ND, J + 1>(d, pos); }
+}
+
+// row i of the pair's element matrix: nd values, either contracted from the geometry factors or read from the cut buffer
 template <int ND, int NP>
-__global__ void __launch_bounds__(RWARPS * 32) k_rows(RowArgs A) {
-  constexpr int NE = ND * ND, PG = 32 / ND, NSLOT = RWARPS * PG;
-  extern __shared__ double smem_rows[];
+__device__ __forceinline__ void row_values(const double *gq, const double *tb, const double *cm, bool iscut, double *v) {
+  constexpr int NE = ND * ND;
+  if (iscut) {
+    if constexpr (ND % 2 == 0) {
+#pragma unroll
+      for (int j = 0; j < ND; j += 2) {
+        const double2 t = __ldg(reinterpret_cast<const double2 *>(cm + j));
+        v[j] = t.x; v[j + 1] = t.y;
+      }
+    } else {
+#pragma unroll
+      for (int j = 0; j < ND; j++) v[j] = __ldg(cm + j);
+    }
+    return;
+  }
+#pragma unroll
+  for (int j = 0; j < ND; j++) v[j] = 0.0;
+#pragma unroll
+  for (int q = 0; q <= NP; q++) {
+    if constexpr (ND % 2 == 0) {
+#pragma unroll
+      for (int j = 0; j < ND; j += 2) {
+        const double2 t = *reinterpret_cast<const double2 *>(tb + q * NE + j);
+        v[j] += gq[q] * t.x; v[j + 1] += gq[q] * t.y;
+      }
+    } else {
+#pragma unroll
+      for (int j = 0; j < ND; j++) v[j] += gq[q] * tb[q * NE + j];
+    }
+  }
+}
+
+template <int ND, int NP>
+__global__ void __launch_bounds__(RT) k_rows(RowArgs A) {
+  constexpr int NE = ND * ND;
+  extern __shared__ __align__(16) double smem_rows[];
   double *tab = smem_rows;                       // [(NP+1)][NE]
   double *acc = smem_rows + (NP + 1) * NE;        // [ACC] values of the chunk's rows
-  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   for (int t = threadIdx.x; t < (NP + 1) * NE; t += blockDim.x) tab[t] = A.tab[t];
-  const int g = lane / ND, j = lane - g * ND;
-  const bool lane_on = g < PG;
-  const int slot = warp * PG + g;
-  const int wsel = (5 + j) >> 2, wsh = ((5 + j) & 3) * 8;   // descriptor word / shift of pos[j]
-  for (int64_t c = blockIdx.x; c < A.nchunks; c += gridDim.x) {
+  for (int64_t cc = blockIdx.x; cc < A.nchunks; cc += gridDim.x) {
+    const int c = __ldg(A.chunk_order + cc);
     const int q0 = __ldg(A.chunk_q + c), q1 = __ldg(A.chunk_q + c + 1);
-    if (q0 == q1) continue;
     const int64_t z0 = __ldg(A.rowptr + __ldg(A.rows + q0));
     const int zlen = (int)(__ldg(A.rowptr + __ldg(A.rows + q1 - 1) + 1) - z0);
+    // this thread's rows [qa, qb) (pair-balanced split from the plan) and pairs [pcur, plast)
+    const int32_t *split = A.chunk_split + (int64_t)c * (RT + 1);
+    const int qa = __ldg(split + threadIdx.x), qb = __ldg(split + threadIdx.x + 1);
+    int q = qa;
+    uint32_t pcur = 0, pend = 0, plast = 0;
+    int off = 0;
+    RowRec recn{0, 0, 0};
+    uint4 d1 = make_uint4(0u, 0u, 0u, 0u), d2 = d1;
+    double2 g1[4];
+    g1[0] = g1[1] = g1[2] = g1[3] = make_double2(0.0, 0.0);
+    if (qa < qb) {
+      const RowRec rec = ld_rowrec(A.rowrec + qa), recl = ld_rowrec(A.rowrec + qb - 1);
+      pcur = rec.p0; pend = rec.p0 + rec.np; off = rec.off; plast = recl.p0 + recl.np;
+      recn = (qa + 1 < qb) ? ld_rowrec(A.rowrec + qa + 1) : rec;
+      d1 = __ldg(A.desc + pcur);
+      if (pcur + 1 < plast) d2 = __ldg(A.desc + pcur + 1);
+      const double2 *Gk = reinterpret_cast<const double2 *>(A.G + (int64_t)(int)d1.x * GSTRIDE);
+#pragma unroll
+      for (int m = 0; m < 4; m++) g1[m] = __ldg(Gk + m);
+    }
     __syncthreads();                               // tab loaded / previous chunk streamed out
     if (A.accumulate) for (int t = threadIdx.x; t < zlen; t += blockDim.x) acc[t] = A.vals[z0 + t];
     else for (int t = threadIdx.x; t < zlen; t += blockDim.x) acc[t] = 0.0;
     __syncthreads();
-    int q = q0 + slot;
-    uint32_t pcur = 0, pend = 0;
-    int off = 0;
-    for (;;) {
-      if (lane_on && pcur == pend && q < q1) {
-        const RowRec rec = A.rowrec[q];
-        pcur = rec.p0; pend = rec.p0 + rec.np; off = rec.off;
-        q += NSLOT;
+    while (pcur < plast) {
+      const uint4 d = d1;
+      double gq[NP + 1];
+      if constexpr (NP == 6) { gq[0] = g1[0].x; gq[1] = g1[0].y; gq[2] = g1[1].x; gq[3] = g1[1].y; gq[4] = g1[2].x; gq[5] = g1[2].y; gq[6] = g1[3].x; }
+      else { gq[0] = g1[0].x; gq[1] = g1[0].y; gq[2] = g1[1].x; gq[3] = g1[3].x; }
+      const long long code = __double_as_longlong(g1[3].y);
+      if (pcur == pend) {                          // first pair of the next row
+        q++;
+        pend = recn.p0 + recn.np; off = recn.off;
+        if (q + 1 < qb) recn = ld_rowrec(A.rowrec + q + 1);
       }
-      const bool work = lane_on && pcur < pend;
-      if (!__any_sync(0xffffffffu, work)) break;
-      if (work) {
-        const uint4 d = __ldg(A.desc + pcur);
-        const int k = (int)d.x, i = (int)(d.y & 0xffu);
-        const uint32_t w = wsel == 1 ? d.y : (wsel == 2 ? d.z : d.w);
-        const int pos = (int)((w >> wsh) & 0xffu);
-        const double2 *Gk = reinterpret_cast<const double2 *>(A.G + (int64_t)k * GSTRIDE);
-        const double2 g3 = __ldg(Gk + 3);
-        const long long code = __double_as_longlong(g3.y);
-        const int ij = i * ND + j;
-        if (code == 0) {
-          const double2 g0 = __ldg(Gk), g1 = __ldg(Gk + 1);
-          const double *t = tab + ij;
-          double v;
-          if constexpr (NP == 6) {
-            const double2 g2 = __ldg(Gk + 2);
-            v = g0.x * t[0] + g0.y * t[NE] + g1.x * t[2 * NE] + g1.y * t[3 * NE] + g2.x * t[4 * NE] + g2.y * t[5 * NE] + g3.x * t[6 * NE];
-          } else {
-            v = g0.x * t[0] + g0.y * t[NE] + g1.x * t[2 * NE] + g3.x * t[3 * NE];
-          }
-          acc[off + pos] += v;
-        } else if (code > 0) {
-          acc[off + pos] += __ldg(A.cutmats + (code - 1) * NE + ij);
-        }
-        pcur++;
+      if (pcur + 1 < plast) {                      // advance the prefetch pipeline
+        d1 = d2;
+        const double2 *Gk = reinterpret_cast<const double2 *>(A.G + (int64_t)(int)d1.x * GSTRIDE);
+#pragma unroll
+        for (int m = 0; m < 4; m++) g1[m] = __ldg(Gk + m);
+        if (pcur + 2 < plast) d2 = __ldg(A.desc + pcur + 2);
       }
-      __syncwarp();
+      if (code >= 0) {
+        const int i = (int)(d.y & 0xffu);
+        const bool iscut = code > 0;
+        const double *cm = A.cutmats + (iscut ? (code - 1) * NE + i * ND : 0);
+        double v[ND], a[ND];
+        int pos[ND];
+        desc_positions<ND, 0>(d, pos);
+        double *accrow = acc + off;
+        // the nd columns of an element are distinct: read all, add, write all (no serialised read-modify-write chain)
+#pragma unroll
+        for (int j = 0; j < ND; j++) a[j] = accrow[pos[j]];
+        row_values<ND, NP>(gq, tab + i * ND, cm, iscut, v);
+#pragma unroll
+        for (int j = 0; j < ND; j++) accrow[pos[j]] = a[j] + v[j];
+      }
+      pcur++;
     }
     __syncthreads();
     for (int t = threadIdx.x; t < zlen; t += blockDim.x) A.vals[z0 + t] = acc[t];
@@ -211,10 +314,10 @@ static int launch_rows_t(const RowArgs &A, int sm_count, cudaStream_t st) {
   auto kern = k_rows<ND, NP>;
   NGSX_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   int occ = 0;
-  NGSX_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, kern, RWARPS * 32, smem));
+  NGSX_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, kern, RT, smem));
   if (occ < 1) { set_error("row kernel does not fit on an SM"); return NGSX_ERR_CUDA; }
   unsigned grid = (unsigned)std::max<int64_t>(1, std::min<int64_t>(A.nchunks, (int64_t)sm_count * occ));
-  kern<<<grid, RWARPS * 32, smem, st>>>(A);
+  kern<<<grid, RT, smem, st>>>(A);
   NGSX_LAUNCH_CHECK();
   return NGSX_OK;
 }
@@ -231,7 +334,7 @@ int rows_scratch(ngsx_rowplan *P, int npairtab) {
 
 int launch_rows(const ngsx_rowplan *P, int npairtab, int accumulate, double *vals, int sm_count, cudaStream_t st) {
   if (P->nrows == 0) return NGSX_OK;
-  RowArgs A{P->nchunks, P->chunk_q, P->rows, P->rowrec, reinterpret_cast<const uint4 *>(P->desc), P->rowptr, P->G, P->cutmats, P->tab,
+  RowArgs A{P->nchunks_active, P->chunk_order, P->chunk_q, P->chunk_split, P->rows, P->rowrec, reinterpret_cast<const uint4 *>(P->desc), P->rowptr, P->G, P->cutmats, P->tab,
             vals, accumulate};
   switch (P->nd * 10 + npairtab) {
     case 33: return launch_rows_t<3, 3>(A, sm_count, st);
@@ -252,7 +355,7 @@ extern "C" {
 int ngsx_rowplan_destroy(ngsx_rowplan *P) {
   if (!P) return NGSX_OK;
   cudaDeviceSynchronize();
-  cudaFree(P->rows); cudaFree(P->pairptr); cudaFree(P->desc); cudaFree(P->rowrec); cudaFree(P->chunk_q);
+  cudaFree(P->rows); cudaFree(P->pairptr); cudaFree(P->desc); cudaFree(P->rowrec); cudaFree(P->chunk_q); cudaFree(P->chunk_order); cudaFree(P->chunk_split);
   cudaFree(P->G); cudaFree(P->cutlist); cudaFree(P->cutcount); cudaFree(P->cutmats); cudaFree(P->tab);
   delete P;
   return NGSX_OK;
@@ -346,10 +449,29 @@ int ngsx_rowplan_create(int64_t nlist, int32_t nd, const int32_t *table, int64_t
     PLAN_CUDA(cudaMalloc(&P->rowrec, nrows * sizeof(RowRec)));
     k_plan_chunks<<<(unsigned)((P->nchunks + 1 + 255) / 256), 256, 0, st>>>(P->nchunks, nrows, P->nnz_lo, P->rows, rowptr, P->chunk_q);
     k_plan_rowrec<<<(unsigned)((nrows + 255) / 256), 256, 0, st>>>(nrows, P->nnz_lo, P->rows, P->pairptr, rowptr, P->chunk_q, P->rowrec, d_bad);
-    g_launches.fetch_add(2);
+    PLAN_CUDA(cudaMalloc(&P->chunk_split, P->nchunks * (RT + 1) * sizeof(int32_t)));
+    k_chunk_split<<<(unsigned)((P->nchunks * (RT + 1) + 255) / 256), 256, 0, st>>>(P->nchunks, P->chunk_q, P->pairptr, P->chunk_split);
+    // chunk processing order
+    uint32_t *ck = nullptr, *ck2 = nullptr;
+    int32_t *ci2 = nullptr;
+    PLAN_CUDA(cudaMalloc(&ck, P->nchunks * sizeof(uint32_t)));
+    PLAN_CUDA(cudaMalloc(&ck2, P->nchunks * sizeof(uint32_t)));
+    PLAN_CUDA(cudaMalloc(&ci2, P->nchunks * sizeof(int32_t)));
+    PLAN_CUDA(cudaMalloc(&P->chunk_order, P->nchunks * sizeof(int32_t)));
+    PLAN_CUDA(cudaMemsetAsync(d_stat, 0, sizeof(unsigned long long), st));
+    k_chunk_keys<<<(unsigned)((P->nchunks + 255) / 256), 256, 0, st>>>(P->nchunks, P->chunk_q, P->pairptr, P->desc, P->ds, ck, ci2, d_stat);
+    cudaFree(tmp); tmp = nullptr; tmp_bytes = 0;
+    PLAN_CUDA(cub::DeviceRadixSort::SortPairs(nullptr, tmp_bytes, ck, ck2, ci2, P->chunk_order, (int)P->nchunks, 0, 32, st));
+    PLAN_CUDA(cudaMalloc(&tmp, tmp_bytes));
+    PLAN_CUDA(cub::DeviceRadixSort::SortPairs(tmp, tmp_bytes, ck, ck2, ci2, P->chunk_order, (int)P->nchunks, 0, 32, st));
+    g_launches.fetch_add(5);
+    unsigned long long nonempty = 0;
+    PLAN_CUDA(cudaMemcpyAsync(&nonempty, d_stat, sizeof nonempty, cudaMemcpyDeviceToHost, st));
     PLAN_CUDA(cudaMemcpyAsync(&bad, d_bad, sizeof bad, cudaMemcpyDeviceToHost, st));
     PLAN_CUDA(cudaStreamSynchronize(st));
+    cudaFree(ck); cudaFree(ck2); cudaFree(ci2);
     PLAN_CUDA(cudaGetLastError());
+    P->nchunks_active = (int64_t)nonempty;
   }
 #undef PLAN_CUDA
   cleanup();

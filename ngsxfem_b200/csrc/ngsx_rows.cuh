@@ -18,7 +18,9 @@ struct ngsx_rowplan {
   uint8_t *desc = nullptr;          // [npairs][ds]
   ngsx::RowRec *rowrec = nullptr;   // [nrows]
   int32_t *chunk_q = nullptr;       // [nchunks + 1] first plan row of each chunk
-  int64_t nchunks = 0;
+  int32_t *chunk_split = nullptr;   // [nchunks][RT + 1] first plan row of each thread's row range (pair-balanced)
+  int32_t *chunk_order = nullptr;   // [nchunks] processing order, non-empty chunks first
+  int64_t nchunks = 0, nchunks_active = 0;
   const int64_t *rowptr = nullptr;  // caller-owned CSR (must outlive the plan)
   // scratch of the numeric phase, allocated on first use
   double *G = nullptr;              // [nlist][8] geometry factors + code
