@@ -8,8 +8,8 @@
 // (56 B, L2-resident) contracted with per-CTA reference tables; cut elements read their row of a compact element-matrix
 // buffer produced by the quadrature kernel.  No colouring, no zero-fill, no read-modify-write, no floating-point atomics.
 //
-// Work decomposition of the row kernel: CTA = chunk of consecutive rows (values in shared memory), one thread per
-// contiguous range of rows (see k_rows).
+// Work decomposition of the row kernel: warp = tile of consecutive rows (values in the warp's shared-memory window), lane =
+// contiguous range of the tile's rows (see k_rows).
 // HBM traffic per P2 tet pair: 16 B descriptor + (L2) 64 B factors; per CSR entry: 8 B written once.
 #include <cub/cub.cuh>
 #include <thrust/iterator/counting_iterator.h>
@@ -17,10 +17,9 @@
 
 namespace ngsx {
 
-constexpr int RT = 256;           // threads per CTA of the row kernel
+constexpr int RW = 4;             // warps per CTA of the row kernel
 constexpr int MAXROW = 256;       // longest supported CSR row (column positions are bytes)
-constexpr int CHW = 7936;         // chunk window in CSR entries: a chunk holds the rows that START inside one window
-constexpr int ACC = CHW + MAXROW; // shared-memory accumulator of a chunk (64 KB)
+constexpr int ACCW = 1536;        // doubles of shared memory per warp: the CSR span of one tile (12 KB)
 
 // ---- plan construction --------------------------------------------------------------------------------------------
 __global__ void __launch_bounds__(256) k_pair_keys(int64_t npairs, const int32_t *__restrict__ table, int64_t row_lo, int64_t row_hi,
@@ -89,63 +88,30 @@ __global__ void __launch_bounds__(256) k_plan_desc(int64_t npairs, int nd, int d
   d[5 + j] = (uint8_t)pos;
 }
 
-// chunk c = plan rows whose first CSR entry lies in [nnz_lo + c CHW, nnz_lo + (c+1) CHW): first such row by binary search
-__global__ void __launch_bounds__(256) k_plan_chunks(int64_t nchunks, int64_t nrows, int64_t nnz_lo, const int32_t *__restrict__ rows,
-                                                    const int64_t *__restrict__ rowptr, int32_t *__restrict__ chunk_q) {
+// tile t = plan rows whose first CSR entry lies in [nnz_lo + t chw, nnz_lo + (t+1) chw): first such row by binary search.
+// chw = ACCW - (longest row), so the span of a tile never exceeds the ACCW doubles a warp owns in shared memory.
+__global__ void __launch_bounds__(256) k_plan_tiles(int64_t ntiles, int64_t nrows, int64_t nnz_lo, int chw, const int32_t *__restrict__ rows,
+                                                   const int64_t *__restrict__ rowptr, int32_t *__restrict__ tile_q) {
   int64_t c = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-  if (c > nchunks) return;
-  if (c == nchunks) { chunk_q[c] = (int32_t)nrows; return; }
-  const int64_t target = nnz_lo + c * CHW;
+  if (c > ntiles) return;
+  if (c == ntiles) { tile_q[c] = (int32_t)nrows; return; }
+  const int64_t target = nnz_lo + c * chw;
   int64_t lo = 0, hi = nrows;
   while (lo < hi) {
     int64_t mid = (lo + hi) >> 1;
     if (rowptr[rows[mid]] < target) lo = mid + 1; else hi = mid;
   }
-  chunk_q[c] = (int32_t)lo;
+  tile_q[c] = (int32_t)lo;
 }
 
-// thread t of the CTA that owns chunk c walks rows [split[t], split[t+1]): the chunk's pairs are cut into RT equal parts
-// and every cut is moved to the next row boundary
-__global__ void __launch_bounds__(256) k_chunk_split(int64_t nchunks, const int32_t *__restrict__ chunk_q, const int64_t *__restrict__ pairptr,
-                                                    int32_t *__restrict__ split) {
-  int64_t t = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-  if (t >= nchunks * (RT + 1)) return;
-  const int64_t c = t / (RT + 1);
-  const int k = (int)(t - c * (RT + 1));
-  const int q0 = chunk_q[c], q1 = chunk_q[c + 1];
-  if (k == RT || q0 == q1) { split[t] = k == RT ? q1 : q0; return; }
-  const int64_t pa = pairptr[q0], pb = pairptr[q1];
-  const int64_t target = pa + ((pb - pa) * k) / RT;
-  int lo = q0, hi = q1;
-  while (lo < hi) {
-    int mid = (lo + hi) >> 1;
-    if (pairptr[mid] < target) lo = mid + 1; else hi = mid;
-  }
-  split[t] = lo;
-}
-
-// processing order of the chunks: by the list index of the first contributing element, so that the vertex-row and edge-row
-// chunks of one mesh region run at about the same time; empty chunks get the largest key
-__global__ void __launch_bounds__(256) k_chunk_keys(int64_t nchunks, const int32_t *__restrict__ chunk_q, const int64_t *__restrict__ pairptr,
-                                                   const uint8_t *__restrict__ desc, int ds, uint32_t *__restrict__ keys, int32_t *__restrict__ ids,
-                                                   unsigned long long *__restrict__ nonempty) {
-  int64_t c = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-  if (c >= nchunks) return;
-  int q0 = chunk_q[c], q1 = chunk_q[c + 1];
-  ids[c] = (int32_t)c;
-  if (q0 == q1) { keys[c] = 0xffffffffu; return; }
-  keys[c] = (uint32_t)*reinterpret_cast<const int32_t *>(desc + pairptr[q0] * ds);
-  atomicAdd(nonempty, 1ULL);
-}
-
-__global__ void __launch_bounds__(256) k_plan_rowrec(int64_t nrows, int64_t nnz_lo, const int32_t *__restrict__ rows, const int64_t *__restrict__ pairptr,
-                                                    const int64_t *__restrict__ rowptr, const int32_t *__restrict__ chunk_q,
-                                                    RowRec *__restrict__ rowrec, int *__restrict__ bad) {
+__global__ void __launch_bounds__(256) k_plan_rowrec(int64_t nrows, int64_t nnz_lo, int chw, const int32_t *__restrict__ rows,
+                                                    const int64_t *__restrict__ pairptr, const int64_t *__restrict__ rowptr,
+                                                    const int32_t *__restrict__ tile_q, RowRec *__restrict__ rowrec, int *__restrict__ bad) {
   int64_t q = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (q >= nrows) return;
   const int64_t zr = rowptr[rows[q]];
-  const int64_t c = (zr - nnz_lo) / CHW;
-  const int64_t z0 = rowptr[rows[chunk_q[c]]];
+  const int64_t c = (zr - nnz_lo) / chw;
+  const int64_t z0 = rowptr[rows[tile_q[c]]];
   const int64_t np = pairptr[q + 1] - pairptr[q];
   if (np > 65535) atomicOr(bad, 4);
   RowRec r;
@@ -153,30 +119,49 @@ __global__ void __launch_bounds__(256) k_plan_rowrec(int64_t nrows, int64_t nnz_
   rowrec[q] = r;
 }
 
-// ---- the row kernel ---------------------------------------------------------------------------------------------
-// CTA = one chunk of consecutive CSR rows whose values (<= ACC doubles) live in shared memory: initialised cooperatively
-// (zero, or the current values when accumulating), gathered, and streamed out once with coalesced stores.
-// ONE THREAD PER ROW RANGE: the rows of the chunk are split into RT contiguous ranges, a thread walks the (row, element)
-// pairs of its range in plan order; per pair it contracts the element's 7 geometry factors with row i of the reference
-// tables (nd entries, shared-memory vector loads) and adds them at their positions of the row.  No two threads share a
-// row, so no synchronisation is needed between the cooperative init and the stream-out, and the summation order of every
-// CSR entry is the plan order: bitwise reproducible.  Descriptors are prefetched two pairs ahead, geometry factors one
-// pair ahead, row records one row ahead.
-struct RowArgs {
-  int64_t nchunks;            // non-empty chunks
-  const int32_t *chunk_order; // [nchunks] chunk numbers in processing order (mesh locality: geometry factors stay in L2)
-  const int32_t *chunk_q;     // [.. + 1] first plan row of each chunk
-  const int32_t *chunk_split; // [..][RT + 1] first plan row of each thread's range
-  const int32_t *rows;
-  const RowRec *rowrec;
-  const uint4 *desc;
-  const int64_t *rowptr;
-  const double *G;
-  const double *cutmats;
-  const double *tab;
-  double *vals;
-  int accumulate;
-};
+// processing order of the tiles: by the list index of the first contributing element, so that the vertex-row and edge-row
+// tiles of one mesh region run at about the same time (their geometry factors are then L2 hits); empty tiles sort last
+__global__ void __launch_bounds__(256) k_tile_keys(int64_t ntiles, const int32_t *__restrict__ tile_q, const int64_t *__restrict__ pairptr,
+                                                  const uint8_t *__restrict__ desc, int ds, uint32_t *__restrict__ keys, int32_t *__restrict__ ids,
+                                                  unsigned long long *__restrict__ nonempty) {
+  int64_t c = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (c >= ntiles) return;
+  int q0 = tile_q[c], q1 = tile_q[c + 1];
+  ids[c] = (int32_t)c;
+  if (q0 == q1) { keys[c] = 0xffffffffu; return; }
+  keys[c] = (uint32_t)*reinterpret_cast<const int32_t *>(desc + pairptr[q0] * ds);
+  atomicAdd(nonempty, 1ULL);
+}
+
+// per tile, in processing order: CSR span and the row range of each lane -- the tile's pairs are cut into 32 equal parts
+// and every cut is moved to the next row boundary
+__global__ void __launch_bounds__(256) k_tile_tables(int64_t nact, const int32_t *__restrict__ order, const int32_t *__restrict__ tile_q,
+                                                    const int32_t *__restrict__ rows, const int64_t *__restrict__ rowptr,
+                                                    const int64_t *__restrict__ pairptr, TileInfo *__restrict__ info, int32_t *__restrict__ split) {
+  int64_t t = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (t >= nact * 33) return;
+  const int64_t tt = t / 33;
+  const int k = (int)(t - tt * 33);
+  const int c = order[tt];
+  const int q0 = tile_q[c], q1 = tile_q[c + 1];
+  if (k == 32) {
+    TileInfo ti;
+    ti.z0 = rowptr[rows[q0]];
+    ti.zlen = (int32_t)(rowptr[rows[q1 - 1] + 1] - ti.z0);
+    ti.pad = 0;
+    info[tt] = ti;
+    split[t] = q1;
+    return;
+  }
+  const int64_t pa = pairptr[q0], pb = pairptr[q1];
+  const int64_t target = pa + ((pb - pa) * k) / 32;
+  int lo = q0, hi = q1;
+  while (lo < hi) {
+    int mid = (lo + hi) >> 1;
+    if (pairptr[mid] < target) lo = mid + 1; else hi = mid;
+  }
+  split[t] = lo;
+}
 
 __device__ __forceinline__ RowRec ld_rowrec(const RowRec *p) {
   const uint2 u = __ldg(reinterpret_cast<const uint2 *>(p));
@@ -231,59 +216,94 @@ __device__ __forceinline__ void row_values(const double *gq, const double *tb, c
   }
 }
 
+// ---- the row kernel ---------------------------------------------------------------------------------------------
+// WARP = one tile of consecutive CSR rows whose values (<= ACCW doubles) live in the warp's private shared-memory window:
+// initialised by the warp (zero, or the current values when accumulating), gathered, and streamed out once with coalesced
+// stores.  Warps never wait for each other (no CTA barrier after the table load).
+// LANE = one contiguous range of the tile's rows (pair-balanced split from the plan): the lane walks the (row, element)
+// pairs of its range in plan order; per pair it contracts the element's 7 geometry factors with row i of the reference
+// tables (nd entries, shared-memory vector loads) and adds them at their positions of the row.  No two lanes share a row
+// and the nd columns of one element are distinct, so the summation order of every CSR entry is the plan order: bitwise
+// reproducible, no atomics.  Descriptors are prefetched two pairs ahead, geometry factors one pair ahead, row records one
+// row ahead; the start-up loads of the next tile are issued before the current tile is streamed out.
+struct RowArgs {
+  int64_t ntiles;             // non-empty tiles, in processing order
+  const TileInfo *info;       // [ntiles]
+  const int32_t *split;       // [ntiles][33] first plan row of each lane's range
+  const RowRec *rowrec;
+  const uint4 *desc;
+  const double *G;
+  const double *cutmats;
+  const double *tab;
+  double *vals;
+  int accumulate;
+};
+
+// per-lane walk state over the pairs [pcur, plast) of the rows [q, qb)
+struct LaneState {
+  int q, qb, off;
+  uint32_t pcur, pend, plast;
+  RowRec recn;
+  uint4 d1, d2;
+  double2 g1[4];
+};
+
+__device__ __forceinline__ void lane_start(const RowArgs &A, int64_t tt, int lane, LaneState &S) {
+  const int32_t *split = A.split + tt * 33;
+  S.q = __ldg(split + lane); S.qb = __ldg(split + lane + 1);
+  S.pcur = S.pend = S.plast = 0; S.off = 0;
+  S.recn = RowRec{0, 0, 0};
+  S.d1 = S.d2 = make_uint4(0u, 0u, 0u, 0u);
+  S.g1[0] = S.g1[1] = S.g1[2] = S.g1[3] = make_double2(0.0, 0.0);
+  if (S.q < S.qb) {
+    const RowRec rec = ld_rowrec(A.rowrec + S.q), recl = ld_rowrec(A.rowrec + S.qb - 1);
+    S.pcur = rec.p0; S.pend = rec.p0 + rec.np; S.off = rec.off; S.plast = recl.p0 + recl.np;
+    S.recn = (S.q + 1 < S.qb) ? ld_rowrec(A.rowrec + S.q + 1) : rec;
+    S.d1 = __ldg(A.desc + S.pcur);
+    if (S.pcur + 1 < S.plast) S.d2 = __ldg(A.desc + S.pcur + 1);
+    const double2 *Gk = reinterpret_cast<const double2 *>(A.G + (int64_t)(int)S.d1.x * GSTRIDE);
+#pragma unroll
+    for (int m = 0; m < 4; m++) S.g1[m] = __ldg(Gk + m);
+  }
+}
+
 template <int ND, int NP>
-__global__ void __launch_bounds__(RT) k_rows(RowArgs A) {
+__global__ void __launch_bounds__(RW * 32) k_rows(RowArgs A) {
   constexpr int NE = ND * ND;
   extern __shared__ __align__(16) double smem_rows[];
-  double *tab = smem_rows;                       // [(NP+1)][NE]
-  double *acc = smem_rows + (NP + 1) * NE;        // [ACC] values of the chunk's rows
+  double *tab = smem_rows;                                        // [(NP+1)][NE]
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  double *acc = smem_rows + (NP + 1) * NE + warp * ACCW;           // this warp's window
   for (int t = threadIdx.x; t < (NP + 1) * NE; t += blockDim.x) tab[t] = A.tab[t];
-  for (int64_t cc = blockIdx.x; cc < A.nchunks; cc += gridDim.x) {
-    const int c = __ldg(A.chunk_order + cc);
-    const int q0 = __ldg(A.chunk_q + c), q1 = __ldg(A.chunk_q + c + 1);
-    const int64_t z0 = __ldg(A.rowptr + __ldg(A.rows + q0));
-    const int zlen = (int)(__ldg(A.rowptr + __ldg(A.rows + q1 - 1) + 1) - z0);
-    // this thread's rows [qa, qb) (pair-balanced split from the plan) and pairs [pcur, plast)
-    const int32_t *split = A.chunk_split + (int64_t)c * (RT + 1);
-    const int qa = __ldg(split + threadIdx.x), qb = __ldg(split + threadIdx.x + 1);
-    int q = qa;
-    uint32_t pcur = 0, pend = 0, plast = 0;
-    int off = 0;
-    RowRec recn{0, 0, 0};
-    uint4 d1 = make_uint4(0u, 0u, 0u, 0u), d2 = d1;
-    double2 g1[4];
-    g1[0] = g1[1] = g1[2] = g1[3] = make_double2(0.0, 0.0);
-    if (qa < qb) {
-      const RowRec rec = ld_rowrec(A.rowrec + qa), recl = ld_rowrec(A.rowrec + qb - 1);
-      pcur = rec.p0; pend = rec.p0 + rec.np; off = rec.off; plast = recl.p0 + recl.np;
-      recn = (qa + 1 < qb) ? ld_rowrec(A.rowrec + qa + 1) : rec;
-      d1 = __ldg(A.desc + pcur);
-      if (pcur + 1 < plast) d2 = __ldg(A.desc + pcur + 1);
-      const double2 *Gk = reinterpret_cast<const double2 *>(A.G + (int64_t)(int)d1.x * GSTRIDE);
-#pragma unroll
-      for (int m = 0; m < 4; m++) g1[m] = __ldg(Gk + m);
-    }
-    __syncthreads();                               // tab loaded / previous chunk streamed out
-    if (A.accumulate) for (int t = threadIdx.x; t < zlen; t += blockDim.x) acc[t] = A.vals[z0 + t];
-    else for (int t = threadIdx.x; t < zlen; t += blockDim.x) acc[t] = 0.0;
-    __syncthreads();
-    while (pcur < plast) {
-      const uint4 d = d1;
+  __syncthreads();
+  const int64_t nwarps = (int64_t)gridDim.x * RW;
+  int64_t tt = (int64_t)blockIdx.x * RW + warp;
+  LaneState S;
+  TileInfo ti{0, 0, 0};
+  if (tt < A.ntiles) { ti = A.info[tt]; lane_start(A, tt, lane, S); }
+  while (tt < A.ntiles) {
+    const int64_t z0 = ti.z0;
+    const int zlen = ti.zlen;
+    if (A.accumulate) for (int t = lane; t < zlen; t += 32) acc[t] = A.vals[z0 + t];
+    else for (int t = lane; t < zlen; t += 32) acc[t] = 0.0;
+    __syncwarp();
+    while (S.pcur < S.plast) {
+      const uint4 d = S.d1;
       double gq[NP + 1];
-      if constexpr (NP == 6) { gq[0] = g1[0].x; gq[1] = g1[0].y; gq[2] = g1[1].x; gq[3] = g1[1].y; gq[4] = g1[2].x; gq[5] = g1[2].y; gq[6] = g1[3].x; }
-      else { gq[0] = g1[0].x; gq[1] = g1[0].y; gq[2] = g1[1].x; gq[3] = g1[3].x; }
-      const long long code = __double_as_longlong(g1[3].y);
-      if (pcur == pend) {                          // first pair of the next row
-        q++;
-        pend = recn.p0 + recn.np; off = recn.off;
-        if (q + 1 < qb) recn = ld_rowrec(A.rowrec + q + 1);
+      if constexpr (NP == 6) { gq[0] = S.g1[0].x; gq[1] = S.g1[0].y; gq[2] = S.g1[1].x; gq[3] = S.g1[1].y; gq[4] = S.g1[2].x; gq[5] = S.g1[2].y; gq[6] = S.g1[3].x; }
+      else { gq[0] = S.g1[0].x; gq[1] = S.g1[0].y; gq[2] = S.g1[1].x; gq[3] = S.g1[3].x; }
+      const long long code = __double_as_longlong(S.g1[3].y);
+      if (S.pcur == S.pend) {                      // first pair of the next row
+        S.q++;
+        S.pend = S.recn.p0 + S.recn.np; S.off = S.recn.off;
+        if (S.q + 1 < S.qb) S.recn = ld_rowrec(A.rowrec + S.q + 1);
       }
-      if (pcur + 1 < plast) {                      // advance the prefetch pipeline
-        d1 = d2;
-        const double2 *Gk = reinterpret_cast<const double2 *>(A.G + (int64_t)(int)d1.x * GSTRIDE);
+      if (S.pcur + 1 < S.plast) {                  // advance the prefetch pipeline
+        S.d1 = S.d2;
+        const double2 *Gk = reinterpret_cast<const double2 *>(A.G + (int64_t)(int)S.d1.x * GSTRIDE);
 #pragma unroll
-        for (int m = 0; m < 4; m++) g1[m] = __ldg(Gk + m);
-        if (pcur + 2 < plast) d2 = __ldg(A.desc + pcur + 2);
+        for (int m = 0; m < 4; m++) S.g1[m] = __ldg(Gk + m);
+        if (S.pcur + 2 < S.plast) S.d2 = __ldg(A.desc + S.pcur + 2);
       }
       if (code >= 0) {
         const int i = (int)(d.y & 0xffu);
@@ -292,7 +312,7 @@ __global__ void __launch_bounds__(RT) k_rows(RowArgs A) {
         double v[ND], a[ND];
         int pos[ND];
         desc_positions<ND, 0>(d, pos);
-        double *accrow = acc + off;
+        double *accrow = acc + S.off;
         // the nd columns of an element are distinct: read all, add, write all (no serialised read-modify-write chain)
 #pragma unroll
         for (int j = 0; j < ND; j++) a[j] = accrow[pos[j]];
@@ -300,24 +320,29 @@ __global__ void __launch_bounds__(RT) k_rows(RowArgs A) {
 #pragma unroll
         for (int j = 0; j < ND; j++) accrow[pos[j]] = a[j] + v[j];
       }
-      pcur++;
+      S.pcur++;
     }
-    __syncthreads();
-    for (int t = threadIdx.x; t < zlen; t += blockDim.x) A.vals[z0 + t] = acc[t];
+    // next tile: issue its start-up loads now, they fly while this tile is streamed out
+    tt += nwarps;
+    if (tt < A.ntiles) { ti = A.info[tt]; lane_start(A, tt, lane, S); }
+    __syncwarp();
+    for (int t = lane; t < zlen; t += 32) A.vals[z0 + t] = acc[t];
+    __syncwarp();
   }
 }
 
 template <int ND, int NP>
 static int launch_rows_t(const RowArgs &A, int sm_count, cudaStream_t st) {
   constexpr int NE = ND * ND;
-  size_t smem = (size_t)((NP + 1) * NE + ACC) * sizeof(double);
+  size_t smem = (size_t)((NP + 1) * NE + RW * ACCW) * sizeof(double);
   auto kern = k_rows<ND, NP>;
   NGSX_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   int occ = 0;
-  NGSX_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, kern, RT, smem));
+  NGSX_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, kern, RW * 32, smem));
   if (occ < 1) { set_error("row kernel does not fit on an SM"); return NGSX_ERR_CUDA; }
-  unsigned grid = (unsigned)std::max<int64_t>(1, std::min<int64_t>(A.nchunks, (int64_t)sm_count * occ));
-  kern<<<grid, RT, smem, st>>>(A);
+  int64_t need = (A.ntiles + RW - 1) / RW;
+  unsigned grid = (unsigned)std::max<int64_t>(1, std::min<int64_t>(need, (int64_t)sm_count * occ));
+  kern<<<grid, RW * 32, smem, st>>>(A);
   NGSX_LAUNCH_CHECK();
   return NGSX_OK;
 }
@@ -334,7 +359,7 @@ int rows_scratch(ngsx_rowplan *P, int npairtab) {
 
 int launch_rows(const ngsx_rowplan *P, int npairtab, int accumulate, double *vals, int sm_count, cudaStream_t st) {
   if (P->nrows == 0) return NGSX_OK;
-  RowArgs A{P->nchunks_active, P->chunk_order, P->chunk_q, P->chunk_split, P->rows, P->rowrec, reinterpret_cast<const uint4 *>(P->desc), P->rowptr, P->G, P->cutmats, P->tab,
+  RowArgs A{P->ntiles_active, P->tile_info, P->tile_split, P->rowrec, reinterpret_cast<const uint4 *>(P->desc), P->G, P->cutmats, P->tab,
             vals, accumulate};
   switch (P->nd * 10 + npairtab) {
     case 33: return launch_rows_t<3, 3>(A, sm_count, st);
@@ -355,7 +380,7 @@ extern "C" {
 int ngsx_rowplan_destroy(ngsx_rowplan *P) {
   if (!P) return NGSX_OK;
   cudaDeviceSynchronize();
-  cudaFree(P->rows); cudaFree(P->pairptr); cudaFree(P->desc); cudaFree(P->rowrec); cudaFree(P->chunk_q); cudaFree(P->chunk_order); cudaFree(P->chunk_split);
+  cudaFree(P->rows); cudaFree(P->pairptr); cudaFree(P->desc); cudaFree(P->rowrec); cudaFree(P->tile_q); cudaFree(P->tile_info); cudaFree(P->tile_split);
   cudaFree(P->G); cudaFree(P->cutlist); cudaFree(P->cutcount); cudaFree(P->cutmats); cudaFree(P->tab);
   delete P;
   return NGSX_OK;
@@ -444,34 +469,40 @@ int ngsx_rowplan_create(int64_t nlist, int32_t nd, const int32_t *table, int64_t
   PLAN_CUDA(cudaGetLastError());
   P->nnz_covered = (int64_t)stat[0]; P->max_row = (int64_t)stat[1]; P->nnz_lo = (int64_t)stat[2]; P->nnz_hi = (int64_t)stat[3];
   if (!(bad & 3) && P->max_row <= MAXROW) {
-    P->nchunks = (P->nnz_hi - P->nnz_lo + CHW - 1) / CHW;
-    PLAN_CUDA(cudaMalloc(&P->chunk_q, (P->nchunks + 1) * sizeof(int32_t)));
+    const int chw = ACCW - (int)P->max_row;        // a tile = rows starting inside one window of chw CSR entries: span <= ACCW
+    P->ntiles = (P->nnz_hi - P->nnz_lo + chw - 1) / chw;
+    PLAN_CUDA(cudaMalloc(&P->tile_q, (P->ntiles + 1) * sizeof(int32_t)));
     PLAN_CUDA(cudaMalloc(&P->rowrec, nrows * sizeof(RowRec)));
-    k_plan_chunks<<<(unsigned)((P->nchunks + 1 + 255) / 256), 256, 0, st>>>(P->nchunks, nrows, P->nnz_lo, P->rows, rowptr, P->chunk_q);
-    k_plan_rowrec<<<(unsigned)((nrows + 255) / 256), 256, 0, st>>>(nrows, P->nnz_lo, P->rows, P->pairptr, rowptr, P->chunk_q, P->rowrec, d_bad);
-    PLAN_CUDA(cudaMalloc(&P->chunk_split, P->nchunks * (RT + 1) * sizeof(int32_t)));
-    k_chunk_split<<<(unsigned)((P->nchunks * (RT + 1) + 255) / 256), 256, 0, st>>>(P->nchunks, P->chunk_q, P->pairptr, P->chunk_split);
-    // chunk processing order
+    k_plan_tiles<<<(unsigned)((P->ntiles + 1 + 255) / 256), 256, 0, st>>>(P->ntiles, nrows, P->nnz_lo, chw, P->rows, rowptr, P->tile_q);
+    k_plan_rowrec<<<(unsigned)((nrows + 255) / 256), 256, 0, st>>>(nrows, P->nnz_lo, chw, P->rows, P->pairptr, rowptr, P->tile_q, P->rowrec, d_bad);
+    // tile processing order
     uint32_t *ck = nullptr, *ck2 = nullptr;
-    int32_t *ci2 = nullptr;
-    PLAN_CUDA(cudaMalloc(&ck, P->nchunks * sizeof(uint32_t)));
-    PLAN_CUDA(cudaMalloc(&ck2, P->nchunks * sizeof(uint32_t)));
-    PLAN_CUDA(cudaMalloc(&ci2, P->nchunks * sizeof(int32_t)));
-    PLAN_CUDA(cudaMalloc(&P->chunk_order, P->nchunks * sizeof(int32_t)));
+    int32_t *ci2 = nullptr, *order = nullptr;
+    PLAN_CUDA(cudaMalloc(&ck, P->ntiles * sizeof(uint32_t)));
+    PLAN_CUDA(cudaMalloc(&ck2, P->ntiles * sizeof(uint32_t)));
+    PLAN_CUDA(cudaMalloc(&ci2, P->ntiles * sizeof(int32_t)));
+    PLAN_CUDA(cudaMalloc(&order, P->ntiles * sizeof(int32_t)));
     PLAN_CUDA(cudaMemsetAsync(d_stat, 0, sizeof(unsigned long long), st));
-    k_chunk_keys<<<(unsigned)((P->nchunks + 255) / 256), 256, 0, st>>>(P->nchunks, P->chunk_q, P->pairptr, P->desc, P->ds, ck, ci2, d_stat);
+    k_tile_keys<<<(unsigned)((P->ntiles + 255) / 256), 256, 0, st>>>(P->ntiles, P->tile_q, P->pairptr, P->desc, P->ds, ck, ci2, d_stat);
     cudaFree(tmp); tmp = nullptr; tmp_bytes = 0;
-    PLAN_CUDA(cub::DeviceRadixSort::SortPairs(nullptr, tmp_bytes, ck, ck2, ci2, P->chunk_order, (int)P->nchunks, 0, 32, st));
+    PLAN_CUDA(cub::DeviceRadixSort::SortPairs(nullptr, tmp_bytes, ck, ck2, ci2, order, (int)P->ntiles, 0, 32, st));
     PLAN_CUDA(cudaMalloc(&tmp, tmp_bytes));
-    PLAN_CUDA(cub::DeviceRadixSort::SortPairs(tmp, tmp_bytes, ck, ck2, ci2, P->chunk_order, (int)P->nchunks, 0, 32, st));
+    PLAN_CUDA(cub::DeviceRadixSort::SortPairs(tmp, tmp_bytes, ck, ck2, ci2, order, (int)P->ntiles, 0, 32, st));
     g_launches.fetch_add(5);
     unsigned long long nonempty = 0;
     PLAN_CUDA(cudaMemcpyAsync(&nonempty, d_stat, sizeof nonempty, cudaMemcpyDeviceToHost, st));
     PLAN_CUDA(cudaMemcpyAsync(&bad, d_bad, sizeof bad, cudaMemcpyDeviceToHost, st));
     PLAN_CUDA(cudaStreamSynchronize(st));
-    cudaFree(ck); cudaFree(ck2); cudaFree(ci2);
+    P->ntiles_active = (int64_t)nonempty;
+    PLAN_CUDA(cudaMalloc(&P->tile_info, std::max<int64_t>(1, P->ntiles_active) * sizeof(TileInfo)));
+    PLAN_CUDA(cudaMalloc(&P->tile_split, std::max<int64_t>(1, P->ntiles_active) * 33 * sizeof(int32_t)));
+    if (P->ntiles_active > 0)
+      k_tile_tables<<<(unsigned)((P->ntiles_active * 33 + 255) / 256), 256, 0, st>>>(P->ntiles_active, order, P->tile_q, P->rows, rowptr, P->pairptr,
+                                                                                   P->tile_info, P->tile_split);
+    g_launches.fetch_add(1);
+    PLAN_CUDA(cudaStreamSynchronize(st));
+    cudaFree(ck); cudaFree(ck2); cudaFree(ci2); cudaFree(order);
     PLAN_CUDA(cudaGetLastError());
-    P->nchunks_active = (int64_t)nonempty;
   }
 #undef PLAN_CUDA
   cleanup();

@@ -8,7 +8,8 @@
 //   uint8 i        local row (the dof of the row inside element k)
 //   uint8 pos[nd]  position of local column j inside the CSR row (nd <= 11)
 namespace ngsx {
-struct RowRec { uint32_t p0; uint16_t np; uint16_t off; };   // first pair, number of pairs, offset of the row inside its chunk
+struct RowRec { uint32_t p0; uint16_t np; uint16_t off; };   // first pair, number of pairs, offset of the row inside its tile
+struct TileInfo { int64_t z0; int32_t zlen; int32_t pad; };  // CSR span of a tile
 }
 struct ngsx_rowplan {
   int64_t nlist = 0, ndof = 0, npairs = 0, nrows = 0, nnz_covered = 0, max_row = 0, nnz_lo = 0, nnz_hi = 0;
@@ -17,10 +18,10 @@ struct ngsx_rowplan {
   int64_t *pairptr = nullptr;       // [nrows + 1]
   uint8_t *desc = nullptr;          // [npairs][ds]
   ngsx::RowRec *rowrec = nullptr;   // [nrows]
-  int32_t *chunk_q = nullptr;       // [nchunks + 1] first plan row of each chunk
-  int32_t *chunk_split = nullptr;   // [nchunks][RT + 1] first plan row of each thread's row range (pair-balanced)
-  int32_t *chunk_order = nullptr;   // [nchunks] processing order, non-empty chunks first
-  int64_t nchunks = 0, nchunks_active = 0;
+  int32_t *tile_q = nullptr;        // [ntiles + 1] first plan row of each tile (natural order)
+  ngsx::TileInfo *tile_info = nullptr;  // [ntiles_active] in processing order
+  int32_t *tile_split = nullptr;    // [ntiles_active][33] first plan row of each lane's row range (pair-balanced)
+  int64_t ntiles = 0, ntiles_active = 0;
   const int64_t *rowptr = nullptr;  // caller-owned CSR (must outlive the plan)
   // scratch of the numeric phase, allocated on first use
   double *G = nullptr;              // [nlist][8] geometry factors + code
