@@ -652,9 +652,10 @@ static void launch_ref_tables(const double4 *rule, int nr, double *tab, cudaStre
 // ---------------------------------------------------------------------------------------------------------------
 constexpr int CUTMAT_THREADS = 128;
 
-template <int DIM, int ORDER>
+template <int DIM, int ORDER, bool IFACE>
 __global__ void __launch_bounds__(CUTMAT_THREADS) k_cutmat(ElmatArgs A, int64_t count) {
   constexpr int ND = H1<DIM, ORDER>::ND, NE = ND * ND, NS = ND * (ND + 1) / 2, NEDGE = ND - (DIM + 1);
+  constexpr int NPT = IFACE ? DIM : DIM + 1;       // vertices of a sub-simplex: compile time, so they stay in registers
   extern __shared__ __align__(16) unsigned char smem_raw[];
   double4 *srule_vol = reinterpret_cast<double4 *>(smem_raw);
   double4 *srule_if = srule_vol + A.nr_vol;
@@ -701,7 +702,7 @@ __global__ void __launch_bounds__(CUTMAT_THREADS) k_cutmat(ElmatArgs A, int64_t 
         const double inv = 1.0 / sqrt(g2);
 #pragma unroll
         for (int d = 0; d < DIM; d++) nrm[d] *= inv;
-        if (cut && A.dt == IF) scale = sqrt(g2) / sqrt(r2);           // |F^-T n_ref|
+        if (cut && IFACE) scale = sqrt(g2) / sqrt(r2);                // |F^-T n_ref|
       }
       // normal derivatives of the barycentrics (Nitsche terms)
       double gln[DIM + 1];
@@ -714,20 +715,21 @@ __global__ void __launch_bounds__(CUTMAT_THREADS) k_cutmat(ElmatArgs A, int64_t 
       }
       CutEntry E;
       if (cut) E = lut[mask]; else { E.ns = 1; E.npt = 0; }
-      const double4 *rule = (cut && A.dt == IF) ? srule_if : srule_vol;
-      const int nr = (cut && A.dt == IF) ? A.nr_if : A.nr_vol;
+      const double4 *rule = (cut && IFACE) ? srule_if : srule_vol;
+      const int nr = (cut && IFACE) ? A.nr_if : A.nr_vol;
       for (int sub = 0; sub < E.ns; sub++) {
         double P[4][3];
         double sfac = 1.0;
         if (cut) {
-          for (int v = 0; v < E.npt; v++) coded_point<DIM>(E.v[sub][v], ls, P[v]);
-          sfac = simplex_factor(E.npt, P);
+#pragma unroll
+          for (int v = 0; v < NPT; v++) coded_point<DIM>(E.v[sub][v], ls, P[v]);
+          sfac = simplex_factor(NPT, P);
         }
         const double f0 = meas * sfac * scale;
         for (int q = 0; q < nr; q++) {
           const double4 r = rule[q];
           double xi[3] = {r.x, r.y, r.z};
-          if (cut) simplex_point(E.npt, P, r, xi);
+          if (cut) simplex_point(NPT, P, r, xi);
           double lam[DIM + 1];
           double last = 1.0;
 #pragma unroll
@@ -764,11 +766,11 @@ __global__ void __launch_bounds__(CUTMAT_THREADS) k_cutmat(ElmatArgs A, int64_t 
             const double am = fm * sv[i] + fn * gn[i], an = fn * sv[i];     // (cm phi_i + cn dn phi_i) phi_j + cn phi_i dn phi_j
 #pragma unroll
             for (int j = 0; j <= i; j++) {
-              double v = am * sv[j];
+              double v = fma(am, sv[j], acc[t]);
 #pragma unroll
-              for (int d = 0; d < DIM; d++) v += ag[d] * gv[j][d];
-              if (cn != 0.0) v += an * gn[j];
-              acc[t++] += v;
+              for (int d = 0; d < DIM; d++) v = fma(ag[d], gv[j][d], v);
+              if (cn != 0.0) v = fma(an, gn[j], v);
+              acc[t++] = v;
             }
           }
         }
@@ -787,10 +789,10 @@ __global__ void __launch_bounds__(CUTMAT_THREADS) k_cutmat(ElmatArgs A, int64_t 
   }
 }
 
-template <int DIM, int ORDER>
+template <int DIM, int ORDER, bool IFACE>
 static int launch_cutmat_t(const ElmatArgs &A, int sm_count, int64_t maxcount, cudaStream_t st) {
   size_t smem = (size_t)(A.nr_vol + A.nr_if) * sizeof(double4) + 16 * sizeof(CutEntry);
-  auto kern = k_cutmat<DIM, ORDER>;
+  auto kern = k_cutmat<DIM, ORDER, IFACE>;
   int occ = 0;
   NGSX_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, kern, CUTMAT_THREADS, smem));
   if (occ < 1) { set_error("cut-element kernel does not fit on an SM"); return NGSX_ERR_CUDA; }
@@ -802,11 +804,15 @@ static int launch_cutmat_t(const ElmatArgs &A, int sm_count, int64_t maxcount, c
 }
 
 static int launch_cutmat(const ElmatArgs &A, int fe_order, int sm_count, int64_t maxcount, cudaStream_t st) {
-  switch (A.M.dim * 10 + fe_order) {
-    case 21: return launch_cutmat_t<2, 1>(A, sm_count, maxcount, st);
-    case 22: return launch_cutmat_t<2, 2>(A, sm_count, maxcount, st);
-    case 31: return launch_cutmat_t<3, 1>(A, sm_count, maxcount, st);
-    case 32: return launch_cutmat_t<3, 2>(A, sm_count, maxcount, st);
+  switch (A.M.dim * 100 + fe_order * 10 + (A.dt == IF ? 1 : 0)) {
+    case 210: return launch_cutmat_t<2, 1, false>(A, sm_count, maxcount, st);
+    case 211: return launch_cutmat_t<2, 1, true>(A, sm_count, maxcount, st);
+    case 220: return launch_cutmat_t<2, 2, false>(A, sm_count, maxcount, st);
+    case 221: return launch_cutmat_t<2, 2, true>(A, sm_count, maxcount, st);
+    case 310: return launch_cutmat_t<3, 1, false>(A, sm_count, maxcount, st);
+    case 311: return launch_cutmat_t<3, 1, true>(A, sm_count, maxcount, st);
+    case 320: return launch_cutmat_t<3, 2, false>(A, sm_count, maxcount, st);
+    case 321: return launch_cutmat_t<3, 2, true>(A, sm_count, maxcount, st);
   }
   set_error("unsupported (dim, order)");
   return NGSX_ERR_UNSUPPORTED;

@@ -22,12 +22,15 @@ constexpr int MAXROW = 256;       // longest supported CSR row (column positions
 constexpr int ACCW = 1536;        // doubles of shared memory per warp: the CSR span of one tile (12 KB)
 
 // ---- plan construction --------------------------------------------------------------------------------------------
-__global__ void __launch_bounds__(256) k_pair_keys(int64_t npairs, const int32_t *__restrict__ table, int64_t row_lo, int64_t row_hi,
-                                                  uint64_t *__restrict__ keys) {
+// key = (row, local row i, list index k): the pairs of a row are walked grouped by i, so that the lanes of a warp mostly
+// read the same rows of the reference tables in the same step (shared-memory broadcast instead of distinct wavefronts)
+__global__ void __launch_bounds__(256) k_pair_keys(int64_t npairs, int nd, int64_t nlist, const int32_t *__restrict__ table, int64_t row_lo,
+                                                  int64_t row_hi, uint64_t *__restrict__ keys) {
   int64_t p = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (p >= npairs) return;
   int32_t r = table[p];
-  keys[p] = (r < row_lo || r >= row_hi) ? ~0ULL : (((uint64_t)(uint32_t)r << 32) | (uint64_t)p);
+  const int64_t k = p / nd, i = p - k * nd;
+  keys[p] = (r < row_lo || r >= row_hi) ? ~0ULL : (((uint64_t)(uint32_t)r << 32) | (uint64_t)(i * nlist + k));
 }
 
 __global__ void k_lower_bound(int64_t n, const uint64_t *__restrict__ keys, uint64_t target, int64_t *out) {
@@ -62,7 +65,7 @@ __global__ void __launch_bounds__(256) k_plan_rows(int64_t nrows, int64_t npairs
 }
 
 // one thread per (pair, local column): position of the column inside the CSR row
-__global__ void __launch_bounds__(256) k_plan_desc(int64_t npairs, int nd, int ds, const uint64_t *__restrict__ keys,
+__global__ void __launch_bounds__(256) k_plan_desc(int64_t npairs, int nd, int64_t nlist, int ds, const uint64_t *__restrict__ keys,
                                                   const int32_t *__restrict__ table, const int64_t *__restrict__ rowptr,
                                                   const int32_t *__restrict__ colidx, uint8_t *__restrict__ desc, int *__restrict__ bad) {
   int64_t t = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
@@ -72,8 +75,8 @@ __global__ void __launch_bounds__(256) k_plan_desc(int64_t npairs, int nd, int d
   uint64_t key = keys[pp];
   int32_t r = (int32_t)(key >> 32);
   uint32_t p = (uint32_t)(key & 0xffffffffULL);
-  uint32_t k = p / (uint32_t)nd;
-  int i = (int)(p - k * (uint32_t)nd);
+  int i = (int)(p / (uint32_t)nlist);
+  uint32_t k = p - (uint32_t)i * (uint32_t)nlist;
   int32_t col = table[(int64_t)k * nd + j];
   int64_t rs = rowptr[r], lo = rs, hi = rowptr[r + 1] - 1;
   while (lo < hi) {
@@ -425,7 +428,7 @@ int ngsx_rowplan_create(int64_t nlist, int32_t nd, const int32_t *table, int64_t
   PLAN_CUDA(cudaMalloc(&d_bad, sizeof(int)));
   PLAN_CUDA(cudaMemsetAsync(d_stat, 0, 4 * sizeof(unsigned long long), st));
   PLAN_CUDA(cudaMemsetAsync(d_bad, 0, sizeof(int), st));
-  k_pair_keys<<<(unsigned)((nall + 255) / 256), 256, 0, st>>>(nall, table, row_lo, row_hi, keys);
+  k_pair_keys<<<(unsigned)((nall + 255) / 256), 256, 0, st>>>(nall, nd, nlist, table, row_lo, row_hi, keys);
   cub::DoubleBuffer<uint64_t> db(keys, alt);
   size_t tmp_bytes = 0;
   PLAN_CUDA(cub::DeviceRadixSort::SortKeys(nullptr, tmp_bytes, db, nall, 0, 64, st));
@@ -459,7 +462,7 @@ int ngsx_rowplan_create(int64_t nlist, int32_t nd, const int32_t *table, int64_t
   PLAN_CUDA(cudaMalloc(&P->desc, (size_t)npairs * P->ds));
   PLAN_CUDA(cudaMemsetAsync(P->desc, 0, (size_t)npairs * P->ds, st));
   k_plan_rows<<<(unsigned)((nrows + 255) / 256), 256, 0, st>>>(nrows, npairs, sorted, P->pairptr, rowptr, P->rows, d_stat);
-  k_plan_desc<<<(unsigned)((npairs * nd + 255) / 256), 256, 0, st>>>(npairs, nd, P->ds, sorted, table, rowptr, colidx, P->desc, d_bad);
+  k_plan_desc<<<(unsigned)((npairs * nd + 255) / 256), 256, 0, st>>>(npairs, nd, nlist, P->ds, sorted, table, rowptr, colidx, P->desc, d_bad);
   g_launches.fetch_add(2);
   unsigned long long stat[4];
   int bad = 0;
