@@ -120,6 +120,16 @@ bool rule_lookup(const DeviceData *dd, int sdim, int order, const double4 **ptr,
   return true;
 }
 
+// sum of the weights of the reference rule of a simplex, in table order (host copy of what the kernels sum)
+static double rule_weight_sum(int sdim, int order) {
+  if (order < 0) order = 0;
+  const int *offs = sdim == 1 ? NGSX_RULE_SEGM_OFFS : (sdim == 2 ? NGSX_RULE_TRIG_OFFS : NGSX_RULE_TET_OFFS);
+  const double (*data)[4] = sdim == 1 ? NGSX_RULE_SEGM_DATA : (sdim == 2 ? NGSX_RULE_TRIG_DATA : NGSX_RULE_TET_DATA);
+  double w = 0.0;
+  for (int q = offs[order]; q < offs[order + 1]; q++) w += data[q][3];
+  return w;
+}
+
 static int check_mesh(const ngsx_mesh *m) {
   NGSX_REQUIRE(m != nullptr, "mesh is NULL");
   NGSX_REQUIRE(m->dim == 2 || m->dim == 3, "mesh.dim must be 2 (triangles) or 3 (tetrahedra)");
@@ -367,76 +377,74 @@ __device__ __forceinline__ void map_point(const double (*p)[DIM], const double *
   }
 }
 
-// Integrate: one thread per element for the sign test and the uncut elements; every cut element is then handled by the
-// whole warp (lanes = (sub-simplex, rule point) items), so the few long cut elements do not serialise a warp.  All partial
-// sums have a fixed shape (item -> lane assignment, xor-shuffle tree, block tree, final tree): bitwise reproducible.
+// Integrate in three balanced passes over a per-element scratch array elint[ne]:
+//   1. k_int_uncut: one thread per element -- sign test; uncut elements of the domain write their integral (static reference
+//      rule), the others 0; cut elements are appended to a work list (the list order does not influence any value);
+//   2. k_int_cut:   one warp per listed element, lanes = (sub-simplex, rule point) items, xor-shuffle tree, lane 0 writes
+//      elint[e];
+//   3. k_int_reduce + k_reduce_final: fixed-shape tree over elint.
+// Every partial sum has a shape that depends on ne only: bitwise reproducible, no floating-point atomics.
 template <int DIM>
-__global__ void __launch_bounds__(256) k_integrate(ngsx_mesh M, const double *__restrict__ lset, const CutTable *__restrict__ tab, int dt,
-                                                  const double4 *__restrict__ rule_vol, int nr_vol, const double4 *__restrict__ rule_if, int nr_if,
-                                                  PolyDev f, int fconst, double *__restrict__ partial) {
-  extern __shared__ double4 srule[];               // nr_vol + nr_if
-  __shared__ CutEntry lut[16];
-  __shared__ double wsum[8];
-  __shared__ double wref;                          // sum of the reference weights (constant integrands)
-  for (int i = threadIdx.x; i < nr_vol; i += blockDim.x) srule[i] = rule_vol[i];
-  for (int i = threadIdx.x; i < nr_if; i += blockDim.x) srule[nr_vol + i] = rule_if[i];
-  if (threadIdx.x < 16) lut[threadIdx.x] = tab->e[DIM - 2][dt][threadIdx.x];
-  __syncthreads();
-  if (threadIdx.x == 0) {
-    double w = 0.0;
-    for (int q = 0; q < nr_vol; q++) w += srule[q].w;
-    wref = w;
-  }
-  __syncthreads();
-  const unsigned full = 0xffffffffu;
-  const int lane = threadIdx.x & 31;
-  double sum = 0.0;
-  // fixed grid, block-stride over tiles of blockDim elements: the shape of the reduction does not depend on the device
-  for (int64_t base = (int64_t)blockIdx.x * blockDim.x; base < M.ne; base += (int64_t)gridDim.x * blockDim.x) {
-  const int64_t e = base + threadIdx.x;
-  int dom = -2;
-  if (e < M.ne) {
-    int v[4], mask;
-    double ls[4];
-    load_element<DIM>(M, lset, e, v, ls, (double(*)[DIM]) nullptr);
-    dom = sign_test<DIM>(ls, mask);
-    if (dom == dt && dom != IF) {                  // uncut element inside the domain: the static reference rule
-      double p[DIM + 1][DIM];
+__global__ void __launch_bounds__(256) k_int_uncut(ngsx_mesh M, const double *__restrict__ lset, int dt, const double4 *__restrict__ rule_vol, int nr_vol,
+                                                  PolyDev f, int fconst, double wref, double *__restrict__ elint,
+                                                  int32_t *__restrict__ cutlist, int32_t *__restrict__ cutcount) {
+  const int64_t e = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (e >= M.ne) return;
+  int v[4], mask;
+  double ls[4];
+  load_element<DIM>(M, lset, e, v, ls, (double(*)[DIM]) nullptr);
+  const int dom = sign_test<DIM>(ls, mask);
+  double val = 0.0;
+  if (dom == IF) {
+    cutlist[atomicAdd(cutcount, 1)] = (int32_t)e;
+  } else if (dom == dt) {
+    double p[DIM + 1][DIM];
 #pragma unroll
-      for (int k = 0; k <= DIM; k++)
+    for (int k = 0; k <= DIM; k++)
 #pragma unroll
-        for (int d = 0; d < DIM; d++) p[k][d] = __ldg(M.vert + (int64_t)v[k] * DIM + d);
-      ElGeom<DIM> G;
-      element_geometry<DIM>(p, G);
-      const double meas = fabs(G.det);
-      if (fconst) {
-        sum += meas * (wref * f.c[0]);
-      } else {
-        for (int q = 0; q < nr_vol; q++) {
-          double4 r = srule[q];
-          double xi[3] = {r.x, r.y, r.z}, x[3];
-          map_point<DIM>(p, xi, x);
-          sum += meas * r.w * eval_poly(f, x);
-        }
+      for (int d = 0; d < DIM; d++) p[k][d] = __ldg(M.vert + (int64_t)v[k] * DIM + d);
+    ElGeom<DIM> G;
+    element_geometry<DIM>(p, G);
+    const double meas = fabs(G.det);
+    if (fconst) {
+      val = meas * (wref * f.c[0]);
+    } else {
+      for (int q = 0; q < nr_vol; q++) {
+        const double4 r = rule_vol[q];
+        double xi[3] = {r.x, r.y, r.z}, x[3];
+        map_point<DIM>(p, xi, x);
+        val += meas * r.w * eval_poly(f, x);
       }
     }
   }
-  // cut elements, one after the other, by the whole warp
-  unsigned todo = __ballot_sync(full, dom == IF);
-  while (todo) {
-    const int src = __ffs(todo) - 1;
-    todo &= todo - 1;
-    const int64_t ee = e - lane + src;             // element of lane `src`
+  elint[e] = val;
+}
+
+template <int DIM>
+__global__ void __launch_bounds__(256) k_int_cut(ngsx_mesh M, const double *__restrict__ lset, const CutTable *__restrict__ tab, int dt,
+                                                const double4 *__restrict__ rule_vol, int nr_vol, const double4 *__restrict__ rule_if, int nr_if,
+                                                PolyDev f, int fconst, const int32_t *__restrict__ cutlist, const int32_t *__restrict__ cutcount,
+                                                double *__restrict__ elint) {
+  extern __shared__ double4 srule[];               // the rule of this call: nr points
+  __shared__ CutEntry lut[16];
+  const double4 *grule = dt == IF ? rule_if : rule_vol;
+  const int nr = dt == IF ? nr_if : nr_vol;
+  for (int i = threadIdx.x; i < nr; i += blockDim.x) srule[i] = grule[i];
+  if (threadIdx.x < 16) lut[threadIdx.x] = tab->e[DIM - 2][dt][threadIdx.x];
+  __syncthreads();
+  const unsigned full = 0xffffffffu;
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, wpb = blockDim.x >> 5;
+  const int count = *cutcount;
+  for (int64_t c = (int64_t)blockIdx.x * wpb + warp; c < count; c += (int64_t)gridDim.x * wpb) {
+    const int64_t e = cutlist[c];
     int v[4], mask;
     double ls[4], p[DIM + 1][DIM];
-    load_element<DIM>(M, lset, ee, v, ls, p);      // same address in every lane: one broadcast transaction
+    load_element<DIM>(M, lset, e, v, ls, p);       // same address in every lane: broadcast transactions
     sign_test<DIM>(ls, mask);
     ElGeom<DIM> G;
     element_geometry<DIM>(p, G);
     const double meas = fabs(G.det);
     const CutEntry E = lut[mask];
-    const double4 *rule = dt == IF ? srule + nr_vol : srule;
-    const int nr = dt == IF ? nr_if : nr_vol;
     const double scale = dt == IF ? interface_scale<DIM>(G, ls) : 1.0;
     const int nitems = E.ns * nr;
     double part = 0.0;
@@ -446,23 +454,29 @@ __global__ void __launch_bounds__(256) k_integrate(ngsx_mesh M, const double *__
       for (int k = 0; k < E.npt; k++) coded_point<DIM>(E.v[s][k], ls, P[k]);
       const double fac = simplex_factor(E.npt, P) * scale;
       double xi[3], x[3];
-      const double4 r = rule[q];
+      const double4 r = srule[q];
       simplex_point(E.npt, P, r, xi);
       map_point<DIM>(p, xi, x);
       part += meas * (r.w * fac) * (fconst ? f.c[0] : eval_poly(f, x));
     }
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) part += __shfl_xor_sync(full, part, o);
-    if (lane == src) sum += part;
+    if (lane == 0) elint[e] = part;
   }
-  }
+}
+
+// first reduction level: fixed grid, block-stride over elint, fixed block tree -> one partial per block
+__global__ void __launch_bounds__(256) k_int_reduce(int64_t n, const double *__restrict__ elint, double *__restrict__ partial) {
+  __shared__ double wsum[8];
+  double sum = 0.0;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) sum += elint[i];
 #pragma unroll
-  for (int o = 16; o > 0; o >>= 1) sum += __shfl_xor_sync(full, sum, o);
-  if (lane == 0) wsum[threadIdx.x >> 5] = sum;
+  for (int o = 16; o > 0; o >>= 1) sum += __shfl_xor_sync(0xffffffffu, sum, o);
+  if ((threadIdx.x & 31) == 0) wsum[threadIdx.x >> 5] = sum;
   __syncthreads();
   if (threadIdx.x == 0) {
     double s = 0.0;
-    for (int w = 0; w < (int)(blockDim.x >> 5); w++) s += wsum[w];
+    for (int w = 0; w < 8; w++) s += wsum[w];
     partial[blockIdx.x] = s;
   }
 }
@@ -669,19 +683,33 @@ int ngsx_integrate(const ngsx_mesh *mesh, const double *lset_v, int dt, int orde
   PolyDev f;
   f.n = h_f->nterms;
   for (int m = 0; m < f.n; m++) { f.c[m] = h_f->coef[m]; for (int d = 0; d < 3; d++) f.ex[m][d] = h_f->ex[m][d]; }
-  unsigned nb = std::min(nblocks(mesh->ne, 256), 2368u);     // fixed upper bound (16 x 148): device-independent reduction shape
-  double *partial = nullptr;
-  NGSX_CUDA(cudaMallocAsync(&partial, nb * sizeof(double), st));
-  size_t smem = (size_t)(nv + ni) * sizeof(double4);
   const int fconst = f.n == 1 && f.ex[0][0] == 0 && f.ex[0][1] == 0 && f.ex[0][2] == 0;
-  if (mesh->dim == 2) k_integrate<2><<<nb, 256, smem, st>>>(*mesh, lset_v, dd->cut_table, dt, rv, nv, ri, ni, f, fconst, partial);
-  else k_integrate<3><<<nb, 256, smem, st>>>(*mesh, lset_v, dd->cut_table, dt, rv, nv, ri, ni, f, fconst, partial);
-  g_launches.fetch_add(1);
+  const double wref = rule_weight_sum(mesh->dim, order);
+  const int64_t ne = mesh->ne;
+  const unsigned nred = std::min(nblocks(ne, 256), 2368u);   // fixed upper bound (16 x 148): device-independent reduction shape
+  double *elint = nullptr, *partial = nullptr;
+  int32_t *cutlist = nullptr, *cutcount = nullptr;
+  NGSX_CUDA(cudaMallocAsync(&elint, ne * sizeof(double), st));
+  NGSX_CUDA(cudaMallocAsync(&partial, nred * sizeof(double), st));
+  NGSX_CUDA(cudaMallocAsync(&cutlist, (ne + 1) * sizeof(int32_t), st));
+  cutcount = cutlist + ne;
+  cudaError_t e0 = cudaMemsetAsync(cutcount, 0, sizeof(int32_t), st);
+  const unsigned ncut = (unsigned)std::min<int64_t>((ne + 7) / 8, (int64_t)dd->sm_count * 8);
+  const size_t smem = (size_t)std::max(nv, ni) * sizeof(double4);
+  if (mesh->dim == 2) {
+    k_int_uncut<2><<<nblocks(ne, 256), 256, 0, st>>>(*mesh, lset_v, dt, rv, nv, f, fconst, wref, elint, cutlist, cutcount);
+    k_int_cut<2><<<ncut, 256, smem, st>>>(*mesh, lset_v, dd->cut_table, dt, rv, nv, ri, ni, f, fconst, cutlist, cutcount, elint);
+  } else {
+    k_int_uncut<3><<<nblocks(ne, 256), 256, 0, st>>>(*mesh, lset_v, dt, rv, nv, f, fconst, wref, elint, cutlist, cutcount);
+    k_int_cut<3><<<ncut, 256, smem, st>>>(*mesh, lset_v, dd->cut_table, dt, rv, nv, ri, ni, f, fconst, cutlist, cutcount, elint);
+  }
   cudaError_t e1 = cudaGetLastError();
-  k_reduce_final<<<1, 1024, 0, st>>>(nb, partial, out);
-  g_launches.fetch_add(1);
+  k_int_reduce<<<nred, 256, 0, st>>>(ne, elint, partial);
+  k_reduce_final<<<1, 1024, 0, st>>>(nred, partial, out);
+  g_launches.fetch_add(4);
   cudaError_t e2 = cudaGetLastError();
-  cudaFreeAsync(partial, st);
+  cudaFreeAsync(elint, st); cudaFreeAsync(partial, st); cudaFreeAsync(cutlist, st);
+  NGSX_CUDA(e0);
   NGSX_CUDA(e1);
   NGSX_CUDA(e2);
   return NGSX_OK;
