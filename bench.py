@@ -6,8 +6,8 @@ plus CutInfo classification and the IF / NEG Integrate() reductions (SURVEY.md s
   python bench.py --gpus N --steps K --warmup W            (N > 1: launched by torch.distributed.run, one rank per GPU)
   python bench.py --impl reference ...                      (the reference's own CPU code, oracle/_ref, on the host cores)
 
-One JSON line on rank 0.  A "step" = CutInfo.Update + BilinearForm.Assemble (SetZero + fused rule/elmat/scatter, colour by
-colour) + Integrate(IF) + Integrate(NEG) on device-resident inputs; `value` = HASNEG elements assembled / step time summed
+One JSON line on rank 0.  A "step" = CutInfo.Update + BilinearForm.Assemble (geometry factors, cut-element quadrature, owner-
+computes row gather into CSR) + Integrate(IF) + Integrate(NEG) on device-resident inputs; `value` = HASNEG elements assembled / step time summed
 over ranks; `e2e` = the same step through the Python surface with the level set coming from pinned host memory and the CSR
 values + integrals going back to the host every step."""
 import argparse
@@ -24,6 +24,7 @@ ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
 
 ALGO_BYTES_PER_ELEMENT = 1784          # 184 B in + 100 CSR entries x (8 B read + 8 B write)
+ALGO_BYTES_SCATTER = 1600              # the CSR part of it: what the row-gather kernel (k_rows) replaces
 ALGO_BYTES_CLASSIFY = 56               # 16 B el2v + 32 B level set + 3 bits + 8 B ratio
 METRIC = "cut-element matrices assembled/sec (3D P2 sphere)"
 
@@ -104,20 +105,31 @@ def build_problem(nx, device, rank=0, world=1, group=6):
     hasneg = ci.GetElementsOfType(xfem.HASNEG)
     active = hasneg.nonzero()
     n_total = active.numel()
-    if world > 1:                                       # contiguous block of the active list per rank (slab in cube-major order)
-        lo, hi = rank * n_total // world, (rank + 1) * n_total // world
-        mine = torch.zeros(mesh.ne, dtype=torch.bool, device=device)
-        mine[active[lo:hi]] = True
+    row_range = None
+    if world > 1:
+        # owner-computes partition (ngsxfem_b200/partition.py): rank r owns a contiguous block of CSR rows with 1/world of the
+        # (row, element) pairs and lists every HASNEG element touching them (halo elements are evaluated twice, nothing is exchanged)
+        from ngsxfem_b200 import partition
         from ngsxfem_b200.ngs import BitArray
+        blocks = partition.row_blocks(Vh.el2dof[active], Vh.ndof, world)
+        row_range = blocks[rank]
+        mine_els = partition.elements_touching(Vh.el2dof, active, *row_range)
+        mine = torch.zeros(mesh.ne, dtype=torch.bool, device=device)
+        mine[mine_els] = True
         restr = BitArray.from_bool(mine)
     else:
         restr = hasneg
     u, v = Vh.TnT()
     a = xfem.RestrictedBilinearForm(Vh, element_restriction=restr)
     a.group_size = group
+    a.row_range = row_range
     a += xfem.SymbolicBFI(levelset_domain={"levelset": lsetp1, "domain_type": xfem.NEG}, form=grad(u) * grad(v) + u * v,
                           definedonelements=restr)
-    return dict(mesh=mesh, lsetp1=lsetp1, ci=ci, Vh=Vh, a=a, n_total=n_total, xfem=xfem)
+    mesh_int = mesh                                      # this rank's elements of CutInfo.Update and the Integrate() reductions
+    if world > 1:
+        mesh_int = mesh.element_block(*partition.element_block(mesh.ne, rank, world))
+        ci = xfem.CutInfo(mesh_int, lsetp1)
+    return dict(mesh=mesh, mesh_int=mesh_int, lsetp1=lsetp1, ci=ci, Vh=Vh, a=a, n_total=n_total, xfem=xfem)
 
 
 def run_b200(args):
@@ -138,7 +150,7 @@ def run_b200(args):
     L = _lib.load()
     t0 = time.time()
     P = build_problem(args.nx, dev, rank, world, args.group)
-    mesh, lsetp1, ci, a, xfem = P["mesh"], P["lsetp1"], P["ci"], P["a"], P["xfem"]
+    mesh, lsetp1, ci, a, xfem, mesh_int = P["mesh"], P["lsetp1"], P["ci"], P["a"], P["xfem"], P["mesh_int"]
     a.Assemble()                                         # symbolic phase (graph, colouring, slot map) + first numeric pass
     torch.cuda.synchronize()
     setup_s = time.time() - t0
@@ -157,8 +169,8 @@ def run_b200(args):
         e[1].record()
         a.Assemble()
         e[2].record()
-        s_if = xfem.IntegrateX(lsetp1, mesh, cf=1.0, order=4, domain_type=xfem.IF, sync=False)
-        s_neg = xfem.IntegrateX(lsetp1, mesh, cf=1.0, order=4, domain_type=xfem.NEG, sync=False)
+        s_if = xfem.IntegrateX(lsetp1, mesh_int, cf=1.0, order=4, domain_type=xfem.IF, sync=False)
+        s_neg = xfem.IntegrateX(lsetp1, mesh_int, cf=1.0, order=4, domain_type=xfem.NEG, sync=False)
         e[3].record()
         if record is not None:
             record.append(e)
@@ -176,16 +188,22 @@ def run_b200(args):
     sampler.start()
     launches0 = L.ngsx_launch_count()
     rec = []
+    kern_ms = []                                         # per step: [geometry factors, cut-element matrices, row gather] (CUDA events inside the library)
+    L.ngsx_debug_set_timing(1)
+    tbuf = (ctypes.c_double * 3)()
     t_begin, t_end = ev(), ev()
     t_begin.record()
     for _ in range(args.steps):
         s_if, s_neg = step(rec)
+        if a.assembly == "rows" and L.ngsx_debug_get_timing(tbuf) == 0:      # waits for this step's assemble only
+            kern_ms.append(list(tbuf))
         if world > 1:                                    # the path's only exchange at this tier: scalar Integrate() all-reduce
             sc = torch.cat([s_if, s_neg])
             dist.all_reduce(sc)
     t_end.record()
     barrier()
     launches = L.ngsx_launch_count() - launches0
+    L.ngsx_debug_set_timing(0)
     total_ms = t_begin.elapsed_time(t_end)
     for e in rec:
         stage_ms["classify"].append(e[0].elapsed_time(e[1]))
@@ -223,12 +241,14 @@ def run_b200(args):
     # ---- max over ranks -----------------------------------------------------------------------------------------------
     t = torch.tensor([total_ms, e2e_ms, statistics.mean(stage_ms["classify"]), statistics.mean(stage_ms["assemble"]),
                       statistics.mean(stage_ms["integrate"])], dtype=torch.float64, device=dev)
-    cnt = torch.tensor([n_local, a.mat.nnz, launches], dtype=torch.int64, device=dev)
+    owned_nnz = plan.nnz_covered if hasattr(plan, "nnz_covered") else a.mat.nnz
+    cnt = torch.tensor([0, owned_nnz, launches], dtype=torch.int64, device=dev)
     if world > 1:
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         dist.all_reduce(cnt, op=dist.ReduceOp.SUM)
     total_ms, e2e_ms, cl_ms, as_ms, in_ms = t.tolist()
-    n_global, nnz_global, launches_global = cnt.tolist()
+    _, nnz_global, launches_global = cnt.tolist()
+    n_global = P["n_total"]                              # unique HASNEG elements of the job (halo re-evaluations are not counted)
     if rank != 0:
         if world > 1:
             dist.destroy_process_group()
@@ -236,13 +256,25 @@ def run_b200(args):
     ms_per_step = total_ms / args.steps
     value = n_global / (ms_per_step * 1e-3)
     peak, peak_src = measured_peak()
-    # dominant kernel = the fused assemble kernel (one launch per colour): algorithmic bytes of this rank's launches / their time
+    # dominant kernel = k_rows (the owner-computes row gather).  Its share of the survey's per-element figure is the CSR part
+    # (1600 B: 100 entries read + written by the reference's AddElementMatrix); the whole assemble stage (k_geom + k_cutmat +
+    # k_rows) is reported against the full 1784 B.  Durations: CUDA events on the launch stream, live in this run.
     as_local = statistics.mean(stage_ms["assemble"])
-    achieved = ALGO_BYTES_PER_ELEMENT * n_local / (as_local * 1e-3) / 1e9
+    if kern_ms:
+        geom_ms, cut_ms, rows_ms = (statistics.mean(k[i] for k in kern_ms) for i in range(3))
+    else:
+        geom_ms = cut_ms = None
+        rows_ms = as_local
+    # units of this rank's launches: element matrices scattered = (row, element) pairs / dofs per element (== listed elements at N=1)
+    n_units = plan.npairs / P["Vh"].nd if hasattr(plan, "npairs") else n_local
+    achieved = ALGO_BYTES_SCATTER * n_units / (rows_ms * 1e-3) / 1e9
+    stage_achieved = ALGO_BYTES_PER_ELEMENT * n_units / (as_local * 1e-3) / 1e9
+    info = getattr(plan, "npairs", None)
+    own_bytes = (8 * plan.nnz_covered + 16 * plan.npairs + 64 * n_local) if info is not None else None   # values written once + descriptors + factors
     traffic = None
-    tp = os.path.join(ROOT, "profiles", "r01_assemble_traffic.json")
+    tp = os.path.join(ROOT, "profiles", "r01_rows_traffic.json")
     if os.path.exists(tp):
-        traffic = json.load(open(tp)).get("dram_bytes_per_step")
+        traffic = json.load(open(tp)).get("dram_bytes_per_launch")
     out = {
         "metric": METRIC, "value": value, "unit": "elements/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
         "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f64",
@@ -251,11 +283,16 @@ def run_b200(args):
                                f"assemble-to-CSR ({n_global} HASNEG elements) + CutInfo + Integrate(IF,NEG)",
                    "ne": mesh.ne, "hasneg_elements": n_global, "nnz": nnz_global, "assembly": a.assembly, "group": args.group, "colors": plan.ncolors,
                    "setup_s_untimed": round(setup_s, 2), "stage_ms": {"classify": cl_ms, "assemble": as_ms, "integrate": in_ms},
-                   "l2": "inputs larger than L2 (CSR values + slot map > 1 GB per step vs 126 MB L2); no explicit flush",
-                   "partition": "contiguous blocks of the HASNEG element list per rank; Integrate scalars all-reduced (NCCL)"},
-        "roofline": {"bound": "hbm", "kernel": "k_elmat<3,2,CSR> (fused cut rule + element matrix + CSR +=), all colour launches of a step",
+                   "l2": "inputs larger than L2 (CSR values + pair descriptors + mesh > 1.4 GB touched per step vs 126 MB L2); no explicit flush",
+                   "partition": "owner-computes: contiguous CSR row blocks per rank balanced by (row, element) pairs, halo elements re-evaluated, no interface-row exchange; element blocks for Integrate, scalars all-reduced (NCCL)"},
+        "roofline": {"bound": "hbm", "kernel": "k_rows<10,6> (owner-computes row gather: every CSR value of the assembled operator written once)",
                      "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": traffic,
-                     "peak_source": peak_src, "algorithmic_bytes_per_element": ALGO_BYTES_PER_ELEMENT,
+                     "peak_source": peak_src, "algorithmic_bytes_per_element": ALGO_BYTES_SCATTER,
+                     "kernel_ms": {"k_geom": geom_ms, "k_cutmat": cut_ms, "k_rows": rows_ms},
+                     "assemble_stage": {"achieved": stage_achieved, "frac": stage_achieved / peak, "algorithmic_bytes_per_element": ALGO_BYTES_PER_ELEMENT},
+                     "own_algorithm": None if own_bytes is None else {"bytes_per_launch": own_bytes, "achieved": own_bytes / (rows_ms * 1e-3) / 1e9,
+                                                                    "frac": own_bytes / (rows_ms * 1e-3) / 1e9 / peak,
+                                                                    "note": "minimum traffic of the gather formulation: 8 B per CSR value + 16 B per (row, element) pair + 64 B factors per element"},
                      "classify_gbs": ALGO_BYTES_CLASSIFY * mesh.ne / (cl_ms * 1e-3) / 1e9},
         "e2e": {"value": n_global / (e2e_ms / args.steps * 1e-3), "unit": "elements/s", "h2d_bytes_per_step": int(h_lset.numel() * 8),
                 "d2h_bytes_per_step": int(h_vals.numel() * 8 + 16), "ms_per_step": e2e_ms / args.steps,

@@ -96,6 +96,10 @@ def load():
         fn.argtypes = args
     lib.ngsx_debug_set_fast_path.argtypes = [c_int]
     lib.ngsx_debug_set_fast_path.restype = None
+    lib.ngsx_debug_set_timing.argtypes = [c_int]
+    lib.ngsx_debug_set_timing.restype = None
+    lib.ngsx_debug_get_timing.argtypes = [ctypes.POINTER(c_double)]
+    lib.ngsx_debug_get_timing.restype = c_int
     _LIB = lib
     return lib
 

@@ -819,6 +819,10 @@ static int launch_cutmat(const ElmatArgs &A, int fe_order, int sm_count, int64_t
 }
 
 static int g_use_fast = 1;
+// optional per-kernel timing of the row-gather assembly (bench.py roofline): CUDA events on the launch stream
+static int g_timing = 0;
+static cudaEvent_t g_ev[4];
+static bool g_ev_ready = false;
 
 }  // namespace ngsx
 
@@ -828,6 +832,26 @@ extern "C" {
 
 // test hook: 0 disables the constant-rule path so both paths can be compared on the GPU
 void ngsx_debug_set_fast_path(int on) { g_use_fast = on; }
+
+// measurement hook: when on, ngsx_assemble_csr_rows_h1 records events around its kernels; ngsx_debug_get_timing waits for the
+// last call and returns {geometry factors (+ tables), cut-element matrices, row gather} in milliseconds
+void ngsx_debug_set_timing(int on) {
+  g_timing = on;
+  if (on && !g_ev_ready) {
+    for (auto &e : g_ev) cudaEventCreate(&e);
+    g_ev_ready = true;
+  }
+}
+int ngsx_debug_get_timing(double *h_ms) {
+  NGSX_REQUIRE(h_ms && g_ev_ready, "debug_get_timing: timing was never enabled");
+  NGSX_CUDA(cudaEventSynchronize(g_ev[3]));
+  for (int k = 0; k < 3; k++) {
+    float ms = 0.f;
+    NGSX_CUDA(cudaEventElapsedTime(&ms, g_ev[k], g_ev[k + 1]));
+    h_ms[k] = ms;
+  }
+  return NGSX_OK;
+}
 
 static void fill_form(const ngsx_form_h1 *f, FormDev &d) {
   d.cm = f->c_mass; d.cs = f->c_stiff; d.cn = f->c_nitsche;
@@ -887,6 +911,7 @@ int ngsx_assemble_csr_rows_h1(const ngsx_mesh *mesh, const double *lset_v, int f
   fill_form(h_form, form);
   const int use_fast = g_use_fast && h_form->c_nitsche == 0.0 && dt != IF;
   // 1. reference tables (tiny), 2. geometry factors + quadrature work list, 3. cut-element matrices, 4. row gather
+  if (g_timing) cudaEventRecord(g_ev[0], st);
   switch (dim * 10 + fe_order) {
     case 21: launch_ref_tables<2, 1>(rv, nv, plan->tab, st); break;
     case 22: launch_ref_tables<2, 2>(rv, nv, plan->tab, st); break;
@@ -900,6 +925,7 @@ int ngsx_assemble_csr_rows_h1(const ngsx_mesh *mesh, const double *lset_v, int f
   if (dim == 2) k_geom<2><<<nb, 256, 0, st>>>(*mesh, lset_v, els, nlist, dt, form, use_fast, plan->G, plan->cutlist, plan->cutcount, e);
   else k_geom<3><<<nb, 256, 0, st>>>(*mesh, lset_v, els, nlist, dt, form, use_fast, plan->G, plan->cutlist, plan->cutcount, e);
   NGSX_LAUNCH_CHECK();
+  if (g_timing) cudaEventRecord(g_ev[1], st);
   ElmatArgs A{};
   A.M = *mesh; A.lset = lset_v; A.tab = dd->cut_table; A.dt = dt;
   A.rule_vol = rv; A.nr_vol = nv; A.rule_if = ri; A.nr_if = ni;
@@ -908,7 +934,10 @@ int ngsx_assemble_csr_rows_h1(const ngsx_mesh *mesh, const double *lset_v, int f
   A.elmats = plan->cutmats; A.npts = nullptr;
   // the work-list length lives on the device: launch the persistent grid for the worst case, idle CTAs leave at once
   if (int rc = launch_cutmat(A, fe_order, dd->sm_count, nlist, st)) return rc;
-  return launch_rows(plan, npairtab, accumulate, vals, dd->sm_count, st);
+  if (g_timing) cudaEventRecord(g_ev[2], st);
+  const int rc = launch_rows(plan, npairtab, accumulate, vals, dd->sm_count, st);
+  if (g_timing) cudaEventRecord(g_ev[3], st);
+  return rc;
 }
 
 static int fill_poly(const ngsx_poly *f, PolyDev2 &d) {

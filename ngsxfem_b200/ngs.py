@@ -112,6 +112,13 @@ class Mesh(SimplexMesh):
     def GetNE(self, vb=VOL):
         return self.ne
 
+    def element_block(self, lo: int, hi: int) -> "Mesh":
+        """view on the elements [lo, hi) sharing the vertex array (the per-rank mesh block of element-wise reductions)"""
+        m = Mesh.__new__(Mesh)
+        SimplexMesh.__init__(m, self.dim, self.vert, self.el2v[lo:hi])
+        m._c = None
+        return m
+
     @property
     def nfacet(self):
         return self.facets()[1].shape[0]

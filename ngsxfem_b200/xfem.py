@@ -519,7 +519,9 @@ class BilinearForm:
             self._plans.clear()
         plans = [self._plan_for(k, integ) for k, integ in enumerate(self.integrators)]
         # a single row plan that covers every stored entry overwrites its rows: no SetZero pass, each value written once
-        overwrite = len(plans) == 1 and isinstance(plans[0], _RowPlan) and plans[0].nnz_covered == self.mat.nnz
+        # (with a row range: the rank's rows are one contiguous CSR span, the other rows belong to other ranks and stay untouched)
+        overwrite = len(plans) == 1 and isinstance(plans[0], _RowPlan) and \
+            plans[0].nnz_covered == (self.mat.nnz if self.row_range is None else plans[0].nnz_hi - plans[0].nnz_lo)
         if not overwrite:
             self.mat.vals.zero_()
         if self._err.shape[0] < len(plans):
