@@ -212,7 +212,8 @@ def run_b200(args):
 
     # ---- e2e: level set from pinned host memory every step, CSR values + integrals back to the host ----------------
     h_lset = lsetp1.vec.cpu().pin_memory()
-    h_vals = torch.empty(a.mat.nnz, dtype=torch.float64).pin_memory()
+    v_lo, v_hi = (plan.nnz_lo, plan.nnz_hi) if (world > 1 and hasattr(plan, "nnz_lo")) else (0, a.mat.nnz)   # the CSR span this rank owns
+    h_vals = torch.empty(v_hi - v_lo, dtype=torch.float64).pin_memory()
     h_sc = torch.empty(2, dtype=torch.float64).pin_memory()
     from ngsxfem_b200.ngs import GridFunction
     gf_in = GridFunction(lsetp1.space)
@@ -221,7 +222,7 @@ def run_b200(args):
         gf_in.vec.copy_(h_lset, non_blocking=True)                       # H2D: this step's input
         xfem.InterpolateToP1(gf_in, lsetp1)                              # GridFunction branch + clamp
         s_if, s_neg = step(None)
-        h_vals.copy_(a.mat.vals, non_blocking=True)                      # D2H: the assembled operator
+        h_vals.copy_(a.mat.vals[v_lo:v_hi], non_blocking=True)           # D2H: the assembled operator (this rank's rows)
         h_sc.copy_(torch.cat([s_if, s_neg]), non_blocking=True)
         torch.cuda.current_stream().synchronize()
         a.check_degenerate()                                             # the reference throws from inside Assemble; here: after the sync
