@@ -123,6 +123,7 @@ bool rule_lookup(const DeviceData *dd, int sdim, int order, const double4 **ptr,
 // sum of the weights of the reference rule of a simplex, in table order (host copy of what the kernels sum)
 static double rule_weight_sum(int sdim, int order) {
   if (order < 0) order = 0;
+  if (sdim == 0) return 1.0;
   const int *offs = sdim == 1 ? NGSX_RULE_SEGM_OFFS : (sdim == 2 ? NGSX_RULE_TRIG_OFFS : NGSX_RULE_TET_OFFS);
   const double (*data)[4] = sdim == 1 ? NGSX_RULE_SEGM_DATA : (sdim == 2 ? NGSX_RULE_TRIG_DATA : NGSX_RULE_TET_DATA);
   double w = 0.0;
@@ -188,8 +189,9 @@ __global__ void k_lset_cf(int dim, int64_t nv, const double *__restrict__ vert, 
 }
 
 // sum over the sub-simplices of (dt) of the measure factor: the order-0 part volume divided by the rule weight
+// (out of line: only the ~1.5 % cut elements need it, keeping it out of the hot path's register budget)
 template <int DIM>
-__device__ __forceinline__ double part_factor(const CutEntry &E, const double *ls) {
+__device__ __noinline__ double part_factor(const CutEntry &E, const double *ls) {
   double s = 0.0;
   for (int k = 0; k < E.ns; k++) {
     double P[4][3];
@@ -204,9 +206,6 @@ template <int DIM>
 __global__ void __launch_bounds__(256) k_classify(ngsx_mesh M, const double *__restrict__ lset, const CutTable *__restrict__ tab,
                                                  uint32_t *__restrict__ words, int64_t nwords, int8_t *__restrict__ dom_out,
                                                  double *__restrict__ ratio, unsigned long long *__restrict__ err) {
-  __shared__ CutEntry lut[2][16];
-  for (int i = threadIdx.x; i < 32; i += blockDim.x) lut[i / 16][i % 16] = tab->e[DIM - 2][i / 16][i % 16];
-  __syncthreads();
   int64_t e = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
   int dom = -2;                                        // -2: beyond ne
   if (e < M.ne) {
@@ -217,7 +216,7 @@ __global__ void __launch_bounds__(256) k_classify(ngsx_mesh M, const double *__r
     if (ratio) {
       double r = dom == NEG ? 1.0 : 0.0;
       if (dom == IF) {                                 // xfem/cutinfo.cpp:79-91 (the common rule weight cancels)
-        double vn = part_factor<DIM>(lut[NEG][mask], ls), vp = part_factor<DIM>(lut[POS][mask], ls);
+        double vn = part_factor<DIM>(tab->e[DIM - 2][NEG][mask], ls), vp = part_factor<DIM>(tab->e[DIM - 2][POS][mask], ls);
         r = vn / (vn + vp);
       }
       if (dom == -1) r = nan("");
@@ -377,17 +376,17 @@ __device__ __forceinline__ void map_point(const double (*p)[DIM], const double *
   }
 }
 
-// Integrate in three balanced passes over a per-element scratch array elint[ne]:
-//   1. k_int_uncut: one thread per element -- sign test; uncut elements of the domain write their integral (static reference
-//      rule), the others 0; cut elements are appended to a work list (the list order does not influence any value);
-//   2. k_int_cut:   one warp per listed element, lanes = (sub-simplex, rule point) items, xor-shuffle tree, lane 0 writes
-//      elint[e];
-//   3. k_int_reduce + k_reduce_final: fixed-shape tree over elint.
+// Integrate in two passes over a per-element scratch array elint[ne]:
+//   1. k_int_elem: one thread per element, no block prologue, no barrier, no atomics -- sign test, then the element's
+//      integral: uncut elements of the domain use the static reference rule, cut elements walk their sub-simplices and
+//      rule points (decomposition table and rules are read-only global data: L1 broadcasts); constant integrands need no
+//      point loop at all (measure factors x sum of the reference weights);
+//   2. k_int_reduce + k_reduce_final: fixed-shape tree over elint.
 // Every partial sum has a shape that depends on ne only: bitwise reproducible, no floating-point atomics.
 template <int DIM>
-__global__ void __launch_bounds__(256) k_int_uncut(ngsx_mesh M, const double *__restrict__ lset, int dt, const double4 *__restrict__ rule_vol, int nr_vol,
-                                                  PolyDev f, int fconst, double wref, double *__restrict__ elint,
-                                                  int32_t *__restrict__ cutlist, int32_t *__restrict__ cutcount) {
+__global__ void __launch_bounds__(256) k_int_elem(ngsx_mesh M, const double *__restrict__ lset, const CutTable *__restrict__ tab, int dt,
+                                                 const double4 *__restrict__ rule_vol, int nr_vol, const double4 *__restrict__ rule_if, int nr_if,
+                                                 PolyDev f, int fconst, double wref_vol, double wref_if, double *__restrict__ elint) {
   const int64_t e = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (e >= M.ne) return;
   int v[4], mask;
@@ -395,9 +394,7 @@ __global__ void __launch_bounds__(256) k_int_uncut(ngsx_mesh M, const double *__
   load_element<DIM>(M, lset, e, v, ls, (double(*)[DIM]) nullptr);
   const int dom = sign_test<DIM>(ls, mask);
   double val = 0.0;
-  if (dom == IF) {
-    cutlist[atomicAdd(cutcount, 1)] = (int32_t)e;
-  } else if (dom == dt) {
+  if (dom == IF || dom == dt) {
     double p[DIM + 1][DIM];
 #pragma unroll
     for (int k = 0; k <= DIM; k++)
@@ -406,63 +403,41 @@ __global__ void __launch_bounds__(256) k_int_uncut(ngsx_mesh M, const double *__
     ElGeom<DIM> G;
     element_geometry<DIM>(p, G);
     const double meas = fabs(G.det);
-    if (fconst) {
-      val = meas * (wref * f.c[0]);
+    if (dom != IF) {
+      if (fconst) {
+        val = meas * (wref_vol * f.c[0]);
+      } else {
+        for (int q = 0; q < nr_vol; q++) {
+          const double4 r = rule_vol[q];
+          double xi[3] = {r.x, r.y, r.z}, x[3];
+          map_point<DIM>(p, xi, x);
+          val += meas * r.w * eval_poly(f, x);
+        }
+      }
     } else {
-      for (int q = 0; q < nr_vol; q++) {
-        const double4 r = rule_vol[q];
-        double xi[3] = {r.x, r.y, r.z}, x[3];
-        map_point<DIM>(p, xi, x);
-        val += meas * r.w * eval_poly(f, x);
+      const CutEntry E = tab->e[DIM - 2][dt][mask];
+      const double4 *rule = dt == IF ? rule_if : rule_vol;
+      const int nr = dt == IF ? nr_if : nr_vol;
+      const double scale = dt == IF ? interface_scale<DIM>(G, ls) : 1.0;
+      for (int s = 0; s < E.ns; s++) {
+        double P[4][3];
+        for (int k = 0; k < E.npt; k++) coded_point<DIM>(E.v[s][k], ls, P[k]);
+        const double fac = simplex_factor(E.npt, P) * scale;
+        if (fconst) {
+          val += meas * (((dt == IF ? wref_if : wref_vol) * fac) * f.c[0]);
+        } else {
+          for (int q = 0; q < nr; q++) {
+            double xi[3], x[3];
+            const double4 r = rule[q];
+            simplex_point(E.npt, P, r, xi);
+            map_point<DIM>(p, xi, x);
+            val += meas * (r.w * fac) * eval_poly(f, x);
+          }
+        }
       }
     }
   }
   elint[e] = val;
-}
-
-template <int DIM>
-__global__ void __launch_bounds__(256) k_int_cut(ngsx_mesh M, const double *__restrict__ lset, const CutTable *__restrict__ tab, int dt,
-                                                const double4 *__restrict__ rule_vol, int nr_vol, const double4 *__restrict__ rule_if, int nr_if,
-                                                PolyDev f, int fconst, const int32_t *__restrict__ cutlist, const int32_t *__restrict__ cutcount,
-                                                double *__restrict__ elint) {
-  extern __shared__ double4 srule[];               // the rule of this call: nr points
-  __shared__ CutEntry lut[16];
-  const double4 *grule = dt == IF ? rule_if : rule_vol;
-  const int nr = dt == IF ? nr_if : nr_vol;
-  for (int i = threadIdx.x; i < nr; i += blockDim.x) srule[i] = grule[i];
-  if (threadIdx.x < 16) lut[threadIdx.x] = tab->e[DIM - 2][dt][threadIdx.x];
-  __syncthreads();
-  const unsigned full = 0xffffffffu;
-  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, wpb = blockDim.x >> 5;
-  const int count = *cutcount;
-  for (int64_t c = (int64_t)blockIdx.x * wpb + warp; c < count; c += (int64_t)gridDim.x * wpb) {
-    const int64_t e = cutlist[c];
-    int v[4], mask;
-    double ls[4], p[DIM + 1][DIM];
-    load_element<DIM>(M, lset, e, v, ls, p);       // same address in every lane: broadcast transactions
-    sign_test<DIM>(ls, mask);
-    ElGeom<DIM> G;
-    element_geometry<DIM>(p, G);
-    const double meas = fabs(G.det);
-    const CutEntry E = lut[mask];
-    const double scale = dt == IF ? interface_scale<DIM>(G, ls) : 1.0;
-    const int nitems = E.ns * nr;
-    double part = 0.0;
-    for (int it = lane; it < nitems; it += 32) {
-      const int s = it / nr, q = it - s * nr;
-      double P[4][3];
-      for (int k = 0; k < E.npt; k++) coded_point<DIM>(E.v[s][k], ls, P[k]);
-      const double fac = simplex_factor(E.npt, P) * scale;
-      double xi[3], x[3];
-      const double4 r = srule[q];
-      simplex_point(E.npt, P, r, xi);
-      map_point<DIM>(p, xi, x);
-      part += meas * (r.w * fac) * (fconst ? f.c[0] : eval_poly(f, x));
-    }
-#pragma unroll
-    for (int o = 16; o > 0; o >>= 1) part += __shfl_xor_sync(full, part, o);
-    if (lane == 0) elint[e] = part;
-  }
 }
 
 // first reduction level: fixed grid, block-stride over elint, fixed block tree -> one partial per block
@@ -684,32 +659,22 @@ int ngsx_integrate(const ngsx_mesh *mesh, const double *lset_v, int dt, int orde
   f.n = h_f->nterms;
   for (int m = 0; m < f.n; m++) { f.c[m] = h_f->coef[m]; for (int d = 0; d < 3; d++) f.ex[m][d] = h_f->ex[m][d]; }
   const int fconst = f.n == 1 && f.ex[0][0] == 0 && f.ex[0][1] == 0 && f.ex[0][2] == 0;
-  const double wref = rule_weight_sum(mesh->dim, order);
+  const double wref_vol = rule_weight_sum(mesh->dim, order), wref_if = rule_weight_sum(mesh->dim - 1, order);
   const int64_t ne = mesh->ne;
   const unsigned nred = std::min(nblocks(ne, 256), 2368u);   // fixed upper bound (16 x 148): device-independent reduction shape
   double *elint = nullptr, *partial = nullptr;
-  int32_t *cutlist = nullptr, *cutcount = nullptr;
   NGSX_CUDA(cudaMallocAsync(&elint, ne * sizeof(double), st));
   NGSX_CUDA(cudaMallocAsync(&partial, nred * sizeof(double), st));
-  NGSX_CUDA(cudaMallocAsync(&cutlist, (ne + 1) * sizeof(int32_t), st));
-  cutcount = cutlist + ne;
-  cudaError_t e0 = cudaMemsetAsync(cutcount, 0, sizeof(int32_t), st);
-  const unsigned ncut = (unsigned)std::min<int64_t>((ne + 7) / 8, (int64_t)dd->sm_count * 8);
-  const size_t smem = (size_t)std::max(nv, ni) * sizeof(double4);
-  if (mesh->dim == 2) {
-    k_int_uncut<2><<<nblocks(ne, 256), 256, 0, st>>>(*mesh, lset_v, dt, rv, nv, f, fconst, wref, elint, cutlist, cutcount);
-    k_int_cut<2><<<ncut, 256, smem, st>>>(*mesh, lset_v, dd->cut_table, dt, rv, nv, ri, ni, f, fconst, cutlist, cutcount, elint);
-  } else {
-    k_int_uncut<3><<<nblocks(ne, 256), 256, 0, st>>>(*mesh, lset_v, dt, rv, nv, f, fconst, wref, elint, cutlist, cutcount);
-    k_int_cut<3><<<ncut, 256, smem, st>>>(*mesh, lset_v, dd->cut_table, dt, rv, nv, ri, ni, f, fconst, cutlist, cutcount, elint);
-  }
+  if (mesh->dim == 2)
+    k_int_elem<2><<<nblocks(ne, 256), 256, 0, st>>>(*mesh, lset_v, dd->cut_table, dt, rv, nv, ri, ni, f, fconst, wref_vol, wref_if, elint);
+  else
+    k_int_elem<3><<<nblocks(ne, 256), 256, 0, st>>>(*mesh, lset_v, dd->cut_table, dt, rv, nv, ri, ni, f, fconst, wref_vol, wref_if, elint);
   cudaError_t e1 = cudaGetLastError();
   k_int_reduce<<<nred, 256, 0, st>>>(ne, elint, partial);
   k_reduce_final<<<1, 1024, 0, st>>>(nred, partial, out);
-  g_launches.fetch_add(4);
+  g_launches.fetch_add(3);
   cudaError_t e2 = cudaGetLastError();
-  cudaFreeAsync(elint, st); cudaFreeAsync(partial, st); cudaFreeAsync(cutlist, st);
-  NGSX_CUDA(e0);
+  cudaFreeAsync(elint, st); cudaFreeAsync(partial, st);
   NGSX_CUDA(e1);
   NGSX_CUDA(e2);
   return NGSX_OK;
