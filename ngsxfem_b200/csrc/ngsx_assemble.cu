@@ -544,39 +544,59 @@ static int dispatch_elvec(const ElvecArgs &A, int fe_order, int sm_count, int nc
 // q-th pair a <= b, tab[NPAIR][i][j] = sum_r w_r phi_i phi_j, over the reference rule of the requested order
 template <int DIM, int ORDER>
 __global__ void __launch_bounds__(128) k_ref_tables(const double4 *__restrict__ rule, int nr, double *__restrict__ tab) {
-  constexpr int ND = H1<DIM, ORDER>::ND, NE = ND * ND, NPAIR = DIM * (DIM + 1) / 2;
+  constexpr int ND = H1<DIM, ORDER>::ND, NE = ND * ND, CS = RefTab<DIM>::CS;
   double glr[DIM + 1][DIM];
 #pragma unroll
   for (int k = 0; k <= DIM; k++)
 #pragma unroll
     for (int d = 0; d < DIM; d++) glr[k][d] = (k == DIM) ? -1.0 : (k == d ? 1.0 : 0.0);
+  // mass table  Tm[i][j] = sum_r w_r phi_i phi_j
   for (int idx = threadIdx.x; idx < NE; idx += blockDim.x) {
-    int i = idx / ND, j = idx % ND;
-    double acc[NPAIR + 1];
-#pragma unroll
-    for (int k = 0; k <= NPAIR; k++) acc[k] = 0.0;
+    const int i = idx / ND, j = idx % ND;
+    double acc = 0.0;
     for (int q = 0; q < nr; q++) {
-      double4 r = rule[q];
+      const double4 r = rule[q];
       double lam[4] = {r.x, r.y, r.z, 0.0};
       double last = 1.0;
 #pragma unroll
       for (int k = 0; k < DIM; k++) last -= lam[k];
       lam[DIM] = last;
-      double si, sj, gi[DIM], gj[DIM];
-      h1_shape_grad<DIM, ORDER>(i, lam, glr, si, gi);
-      h1_shape_grad<DIM, ORDER>(j, lam, glr, sj, gj);
-      int pr = 0;
-#pragma unroll
-      for (int a = 0; a < DIM; a++)
-#pragma unroll
-        for (int b = a; b < DIM; b++) {
-          acc[pr] += r.w * (a == b ? gi[a] * gj[a] : (gi[a] * gj[b] + gi[b] * gj[a]));
-          pr++;
-        }
-      acc[NPAIR] += r.w * si * sj;
+      acc += r.w * h1_shape<DIM, ORDER>(i, lam) * h1_shape<DIM, ORDER>(j, lam);
     }
-#pragma unroll
-    for (int k = 0; k <= NPAIR; k++) tab[k * NE + idx] = acc[k];
+    tab[idx] = acc;
+  }
+  // gradient-moment table.  The reference gradients of P1/P2 shapes are affine: d_a phi_i = sum_m c_m X_m, X = (1, x, y[, z]);
+  // cM[i][a][n] = sum_m c_m M_mn with the rule's moments M_mn = sum_r w_r X_m X_n.
+  for (int idx = threadIdx.x; idx < ND * DIM; idx += blockDim.x) {
+    const int i = idx / DIM, a = idx % DIM;
+    double c[DIM + 1];
+    {
+      double lam[4] = {0.0, 0.0, 0.0, 0.0};
+      lam[DIM] = 1.0;
+      double sv, g0[DIM];
+      h1_shape_grad<DIM, ORDER>(i, lam, glr, sv, g0);
+      c[0] = g0[a];
+      for (int m = 0; m < DIM; m++) {
+        double l2[4] = {0.0, 0.0, 0.0, 0.0};
+        l2[m] = 1.0;
+        double gm[DIM];
+        h1_shape_grad<DIM, ORDER>(i, l2, glr, sv, gm);
+        c[m + 1] = gm[a] - g0[a];
+      }
+    }
+    for (int n = 0; n <= DIM; n++) {
+      double s = 0.0;
+      for (int m = 0; m <= DIM; m++) {
+        double mom = 0.0;
+        for (int q = 0; q < nr; q++) {
+          const double4 r = rule[q];
+          const double X[4] = {1.0, r.x, r.y, r.z};
+          mom += r.w * X[m] * X[n];
+        }
+        s += c[m] * mom;
+      }
+      tab[RefTab<DIM>::cm_offset(NE) + i * CS + a * (DIM + 1) + n] = s;
+    }
   }
 }
 

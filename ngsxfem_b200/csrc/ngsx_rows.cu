@@ -12,6 +12,7 @@
 // contiguous range of the tile's rows (see k_rows).
 // HBM traffic per P2 tet pair: 16 B descriptor + (L2) 64 B factors; per CSR entry: 8 B written once.
 #include <cub/cub.cuh>
+#include <vector>
 #include <thrust/iterator/counting_iterator.h>
 #include "ngsx_rows.cuh"
 
@@ -19,7 +20,9 @@ namespace ngsx {
 
 constexpr int RW = 4;             // warps per CTA of the row kernel
 constexpr int MAXROW = 256;       // longest supported CSR row (column positions are bytes)
-constexpr int ACCW = 1536;        // doubles of shared memory per warp: the CSR span of one tile (12 KB)
+constexpr int ACCW = 2176;        // doubles of shared memory per warp: the CSR span of one tile (17 KB)
+constexpr int TILE_MAXROWS = 64;  // rows per tile (2 per lane) ...
+constexpr int TILE_MAXPAIRS = 768;// ... and (row, element) pairs per tile (24 per lane)
 
 // ---- plan construction --------------------------------------------------------------------------------------------
 // key = (row, local row i, list index k): the pairs of a row are walked grouped by i, so that the lanes of a warp mostly
@@ -91,35 +94,12 @@ __global__ void __launch_bounds__(256) k_plan_desc(int64_t npairs, int nd, int64
   d[5 + j] = (uint8_t)pos;
 }
 
-// tile t = plan rows whose first CSR entry lies in [nnz_lo + t chw, nnz_lo + (t+1) chw): first such row by binary search.
-// chw = ACCW - (longest row), so the span of a tile never exceeds the ACCW doubles a warp owns in shared memory.
-__global__ void __launch_bounds__(256) k_plan_tiles(int64_t ntiles, int64_t nrows, int64_t nnz_lo, int chw, const int32_t *__restrict__ rows,
-                                                   const int64_t *__restrict__ rowptr, int32_t *__restrict__ tile_q) {
-  int64_t c = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-  if (c > ntiles) return;
-  if (c == ntiles) { tile_q[c] = (int32_t)nrows; return; }
-  const int64_t target = nnz_lo + c * chw;
-  int64_t lo = 0, hi = nrows;
-  while (lo < hi) {
-    int64_t mid = (lo + hi) >> 1;
-    if (rowptr[rows[mid]] < target) lo = mid + 1; else hi = mid;
-  }
-  tile_q[c] = (int32_t)lo;
-}
-
-__global__ void __launch_bounds__(256) k_plan_rowrec(int64_t nrows, int64_t nnz_lo, int chw, const int32_t *__restrict__ rows,
-                                                    const int64_t *__restrict__ pairptr, const int64_t *__restrict__ rowptr,
-                                                    const int32_t *__restrict__ tile_q, RowRec *__restrict__ rowrec, int *__restrict__ bad) {
+__global__ void __launch_bounds__(256) k_row_spans(int64_t nrows, const int32_t *__restrict__ rows, const int64_t *__restrict__ rowptr,
+                                                  int64_t *__restrict__ span) {
   int64_t q = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (q >= nrows) return;
-  const int64_t zr = rowptr[rows[q]];
-  const int64_t c = (zr - nnz_lo) / chw;
-  const int64_t z0 = rowptr[rows[tile_q[c]]];
-  const int64_t np = pairptr[q + 1] - pairptr[q];
-  if (np > 65535) atomicOr(bad, 4);
-  RowRec r;
-  r.p0 = (uint32_t)pairptr[q]; r.np = (uint16_t)np; r.off = (uint16_t)(zr - z0);
-  rowrec[q] = r;
+  const int32_t r = rows[q];
+  span[2 * q] = rowptr[r]; span[2 * q + 1] = rowptr[r + 1];
 }
 
 // processing order of the tiles: by the list index of the first contributing element, so that the vertex-row and edge-row
@@ -185,37 +165,107 @@ template <int ND, int J> __device__ __forceinline__ void desc_positions(const ui
   if constexpr (J < ND) { pos[J] = desc_pos<J>(d); desc_positions<ND, J + 1>(d, pos); }
 }
 
-// row i of the pair's element matrix: nd values, either contracted from the geometry factors or read from the cut buffer
-template <int ND, int NP>
-__device__ __forceinline__ void row_values(const double *gq, const double *tb, const double *cm, bool iscut, double *v) {
-  constexpr int NE = ND * ND;
-  if (iscut) {
-    if constexpr (ND % 2 == 0) {
+// 32-byte global load (sm_100: LDG.E.256): one L1 tag lookup per half geometry record instead of two
+__device__ __forceinline__ void ldg256(const double *p, double *o) {
+  asm volatile("ld.global.nc.v4.f64 {%0, %1, %2, %3}, [%4];" : "=d"(o[0]), "=d"(o[1]), "=d"(o[2]), "=d"(o[3]) : "l"(p));
+}
+
+// Row i of a constant-rule element matrix from the element's geometry factors, by sum factorisation.
+//   A_ij = |J| c_s sum_r w_r (grad phi_i)^T (J^-1 J^-T) (grad phi_j) + |J| c_m sum_r w_r phi_i phi_j
+// The reference gradients of P1/P2 shapes are affine in the reference coordinates, d_a phi_i = sum_m c_iam X_m, so with the
+// rule's moments folded into cM[i][a][n] (k_ref_tables):  w[b][n] = sum_a Ghat_ab cM[i][a][n]  (36 FMAs in 3D) and
+//   vertex j:      A_ij = w[.][0] . grad lam_j
+//   edge (a, b):   A_ij = -1/2 (Q[a][b] + Q[b][a]),  Q[a][k] = grad lam_a . W(., lam_k),  W(b, lam_k) = coefficient of lam_k in w[b][.]
+// Same quadrature as the reference's static rule, re-associated; 12 + nd doubles of table per pair instead of 7 nd.
+template <int DIM, int ORDER>
+__device__ __forceinline__ void row_values(const double *g, const double *cmi, const double *tm, double *v) {
+  constexpr int ND = H1<DIM, ORDER>::ND, NEDGE = H1<DIM, ORDER>::NEDGE;
+  double Gh[DIM][DIM];
+  {
+    int pr = 0;
 #pragma unroll
-      for (int j = 0; j < ND; j += 2) {
-        const double2 t = __ldg(reinterpret_cast<const double2 *>(cm + j));
-        v[j] = t.x; v[j + 1] = t.y;
-      }
-    } else {
+    for (int a = 0; a < DIM; a++)
 #pragma unroll
-      for (int j = 0; j < ND; j++) v[j] = __ldg(cm + j);
-    }
-    return;
+      for (int b = a; b < DIM; b++) { Gh[a][b] = g[pr]; Gh[b][a] = g[pr]; pr++; }
   }
+  double c[DIM][DIM + 1];
+  if constexpr (DIM == 3) {
 #pragma unroll
-  for (int j = 0; j < ND; j++) v[j] = 0.0;
-#pragma unroll
-  for (int q = 0; q <= NP; q++) {
-    if constexpr (ND % 2 == 0) {
-#pragma unroll
-      for (int j = 0; j < ND; j += 2) {
-        const double2 t = *reinterpret_cast<const double2 *>(tb + q * NE + j);
-        v[j] += gq[q] * t.x; v[j + 1] += gq[q] * t.y;
-      }
-    } else {
-#pragma unroll
-      for (int j = 0; j < ND; j++) v[j] += gq[q] * tb[q * NE + j];
+    for (int t = 0; t < 6; t++) {
+      const double2 x = *reinterpret_cast<const double2 *>(cmi + 2 * t);
+      c[(2 * t) / 4][(2 * t) % 4] = x.x; c[(2 * t + 1) / 4][(2 * t + 1) % 4] = x.y;
     }
+  } else {
+#pragma unroll
+    for (int t = 0; t < 3; t++) {
+      const double2 x = *reinterpret_cast<const double2 *>(cmi + 2 * t);
+      c[(2 * t) / 3][(2 * t) % 3] = x.x; c[(2 * t + 1) / 3][(2 * t + 1) % 3] = x.y;
+    }
+  }
+  double w[DIM][DIM + 1];
+#pragma unroll
+  for (int b = 0; b < DIM; b++)
+#pragma unroll
+    for (int n = 0; n <= DIM; n++) {
+      double s = Gh[0][b] * c[0][n];
+#pragma unroll
+      for (int a = 1; a < DIM; a++) s = fma(Gh[a][b], c[a][n], s);
+      w[b][n] = s;
+    }
+  // vertex functions: grad lam_j = e_j (j < DIM), -(1,..,1) (j = DIM)
+  double dsum = 0.0;
+#pragma unroll
+  for (int j = 0; j < DIM; j++) { v[j] = w[j][0]; dsum += w[j][0]; }
+  v[DIM] = -dsum;
+  if constexpr (ORDER == 2) {
+    double Q[DIM + 1][DIM + 1];
+#pragma unroll
+    for (int b = 0; b < DIM; b++) {
+      double last = w[b][0];
+#pragma unroll
+      for (int k = 0; k < DIM; k++) { Q[b][k] = w[b][k + 1]; last -= w[b][k + 1]; }
+      Q[b][DIM] = last;
+    }
+#pragma unroll
+    for (int k = 0; k <= DIM; k++) {
+      double z = Q[0][k];
+#pragma unroll
+      for (int b = 1; b < DIM; b++) z += Q[b][k];
+      Q[DIM][k] = -z;
+    }
+#pragma unroll
+    for (int ed = 0; ed < NEDGE; ed++) {
+      int a, b;
+      edge_vertices<DIM>(ed, a, b);
+      v[DIM + 1 + ed] = -0.5 * (Q[a][b] + Q[b][a]);
+    }
+  }
+  // mass
+  const double gm = g[6];
+  if constexpr (ND % 2 == 0) {
+#pragma unroll
+    for (int j = 0; j < ND; j += 2) {
+      const double2 t = *reinterpret_cast<const double2 *>(tm + j);
+      v[j] = fma(gm, t.x, v[j]); v[j + 1] = fma(gm, t.y, v[j + 1]);
+    }
+  } else {
+#pragma unroll
+    for (int j = 0; j < ND; j++) v[j] = fma(gm, tm[j], v[j]);
+  }
+}
+
+// row i of a quadrature (cut) element matrix: nd contiguous doubles of the cut buffer
+template <int ND>
+__device__ __forceinline__ void row_values_cut(const double *cm, double *v) {
+  if constexpr (ND % 2 == 0) {
+#pragma unroll
+    for (int j = 0; j < ND; j += 2) {
+      const double2 t = __ldg(reinterpret_cast<const double2 *>(cm + j));
+      v[j] = t.x; v[j + 1] = t.y;
+    }
+  } else {
+#pragma unroll
+    for (int j = 0; j < ND; j++) v[j] = __ldg(cm + j);
   }
 }
 
@@ -248,7 +298,7 @@ struct LaneState {
   uint32_t pcur, pend, plast;
   RowRec recn;
   uint4 d1, d2;
-  double2 g1[4];
+  double g1[8];               // geometry record of pair pcur (g1[7] = code)
 };
 
 __device__ __forceinline__ void lane_start(const RowArgs &A, int64_t tt, int lane, LaneState &S) {
@@ -257,27 +307,27 @@ __device__ __forceinline__ void lane_start(const RowArgs &A, int64_t tt, int lan
   S.pcur = S.pend = S.plast = 0; S.off = 0;
   S.recn = RowRec{0, 0, 0};
   S.d1 = S.d2 = make_uint4(0u, 0u, 0u, 0u);
-  S.g1[0] = S.g1[1] = S.g1[2] = S.g1[3] = make_double2(0.0, 0.0);
+#pragma unroll
+  for (int m = 0; m < 8; m++) S.g1[m] = 0.0;
   if (S.q < S.qb) {
     const RowRec rec = ld_rowrec(A.rowrec + S.q), recl = ld_rowrec(A.rowrec + S.qb - 1);
     S.pcur = rec.p0; S.pend = rec.p0 + rec.np; S.off = rec.off; S.plast = recl.p0 + recl.np;
     S.recn = (S.q + 1 < S.qb) ? ld_rowrec(A.rowrec + S.q + 1) : rec;
     S.d1 = __ldg(A.desc + S.pcur);
     if (S.pcur + 1 < S.plast) S.d2 = __ldg(A.desc + S.pcur + 1);
-    const double2 *Gk = reinterpret_cast<const double2 *>(A.G + (int64_t)(int)S.d1.x * GSTRIDE);
-#pragma unroll
-    for (int m = 0; m < 4; m++) S.g1[m] = __ldg(Gk + m);
+    const double *Gk = A.G + (int64_t)(int)S.d1.x * GSTRIDE;
+    ldg256(Gk, S.g1); ldg256(Gk + 4, S.g1 + 4);
   }
 }
 
-template <int ND, int NP>
+template <int DIM, int ORDER>
 __global__ void __launch_bounds__(RW * 32) k_rows(RowArgs A) {
-  constexpr int NE = ND * ND;
+  constexpr int ND = H1<DIM, ORDER>::ND, NE = ND * ND, CS = RefTab<DIM>::CS, CMO = RefTab<DIM>::cm_offset(NE), NTAB = CMO + ND * CS;
   extern __shared__ __align__(16) double smem_rows[];
-  double *tab = smem_rows;                                        // [(NP+1)][NE]
+  double *tab = smem_rows;                                        // mass table [ND][ND], then cM [ND][CS]
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  double *acc = smem_rows + (NP + 1) * NE + warp * ACCW;           // this warp's window
-  for (int t = threadIdx.x; t < (NP + 1) * NE; t += blockDim.x) tab[t] = A.tab[t];
+  double *acc = smem_rows + NTAB + warp * ACCW;                    // this warp's window
+  for (int t = threadIdx.x; t < NTAB; t += blockDim.x) tab[t] = A.tab[t];
   __syncthreads();
   const int64_t nwarps = (int64_t)gridDim.x * RW;
   int64_t tt = (int64_t)blockIdx.x * RW + warp;
@@ -292,10 +342,10 @@ __global__ void __launch_bounds__(RW * 32) k_rows(RowArgs A) {
     __syncwarp();
     while (S.pcur < S.plast) {
       const uint4 d = S.d1;
-      double gq[NP + 1];
-      if constexpr (NP == 6) { gq[0] = S.g1[0].x; gq[1] = S.g1[0].y; gq[2] = S.g1[1].x; gq[3] = S.g1[1].y; gq[4] = S.g1[2].x; gq[5] = S.g1[2].y; gq[6] = S.g1[3].x; }
-      else { gq[0] = S.g1[0].x; gq[1] = S.g1[0].y; gq[2] = S.g1[1].x; gq[3] = S.g1[3].x; }
-      const long long code = __double_as_longlong(S.g1[3].y);
+      double g[8];
+#pragma unroll
+      for (int m = 0; m < 8; m++) g[m] = S.g1[m];
+      const long long code = __double_as_longlong(g[7]);
       if (S.pcur == S.pend) {                      // first pair of the next row
         S.q++;
         S.pend = S.recn.p0 + S.recn.np; S.off = S.recn.off;
@@ -303,15 +353,12 @@ __global__ void __launch_bounds__(RW * 32) k_rows(RowArgs A) {
       }
       if (S.pcur + 1 < S.plast) {                  // advance the prefetch pipeline
         S.d1 = S.d2;
-        const double2 *Gk = reinterpret_cast<const double2 *>(A.G + (int64_t)(int)S.d1.x * GSTRIDE);
-#pragma unroll
-        for (int m = 0; m < 4; m++) S.g1[m] = __ldg(Gk + m);
+        const double *Gk = A.G + (int64_t)(int)S.d1.x * GSTRIDE;
+        ldg256(Gk, S.g1); ldg256(Gk + 4, S.g1 + 4);
         if (S.pcur + 2 < S.plast) S.d2 = __ldg(A.desc + S.pcur + 2);
       }
       if (code >= 0) {
         const int i = (int)(d.y & 0xffu);
-        const bool iscut = code > 0;
-        const double *cm = A.cutmats + (iscut ? (code - 1) * NE + i * ND : 0);
         double v[ND], a[ND];
         int pos[ND];
         desc_positions<ND, 0>(d, pos);
@@ -319,7 +366,8 @@ __global__ void __launch_bounds__(RW * 32) k_rows(RowArgs A) {
         // the nd columns of an element are distinct: read all, add, write all (no serialised read-modify-write chain)
 #pragma unroll
         for (int j = 0; j < ND; j++) a[j] = accrow[pos[j]];
-        row_values<ND, NP>(gq, tab + i * ND, cm, iscut, v);
+        if (code > 0) row_values_cut<ND>(A.cutmats + (code - 1) * NE + i * ND, v);
+        else row_values<DIM, ORDER>(g, tab + CMO + i * CS, tab + i * ND, v);
 #pragma unroll
         for (int j = 0; j < ND; j++) accrow[pos[j]] = a[j] + v[j];
       }
@@ -334,11 +382,11 @@ __global__ void __launch_bounds__(RW * 32) k_rows(RowArgs A) {
   }
 }
 
-template <int ND, int NP>
+template <int DIM, int ORDER>
 static int launch_rows_t(const RowArgs &A, int sm_count, cudaStream_t st) {
-  constexpr int NE = ND * ND;
-  size_t smem = (size_t)((NP + 1) * NE + RW * ACCW) * sizeof(double);
-  auto kern = k_rows<ND, NP>;
+  constexpr int ND = H1<DIM, ORDER>::ND, NTAB = RefTab<DIM>::cm_offset(ND * ND) + ND * RefTab<DIM>::CS;
+  size_t smem = (size_t)(NTAB + RW * ACCW) * sizeof(double);
+  auto kern = k_rows<DIM, ORDER>;
   NGSX_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   int occ = 0;
   NGSX_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, kern, RW * 32, smem));
@@ -365,10 +413,10 @@ int launch_rows(const ngsx_rowplan *P, int npairtab, int accumulate, double *val
   RowArgs A{P->ntiles_active, P->tile_info, P->tile_split, P->rowrec, reinterpret_cast<const uint4 *>(P->desc), P->G, P->cutmats, P->tab,
             vals, accumulate};
   switch (P->nd * 10 + npairtab) {
-    case 33: return launch_rows_t<3, 3>(A, sm_count, st);
-    case 63: return launch_rows_t<6, 3>(A, sm_count, st);
-    case 46: return launch_rows_t<4, 6>(A, sm_count, st);
-    case 106: return launch_rows_t<10, 6>(A, sm_count, st);
+    case 33: return launch_rows_t<2, 1>(A, sm_count, st);
+    case 63: return launch_rows_t<2, 2>(A, sm_count, st);
+    case 46: return launch_rows_t<3, 1>(A, sm_count, st);
+    case 106: return launch_rows_t<3, 2>(A, sm_count, st);
   }
   set_error("row gather: unsupported (dofs per element, dimension)");
   return NGSX_ERR_UNSUPPORTED;
@@ -472,12 +520,45 @@ int ngsx_rowplan_create(int64_t nlist, int32_t nd, const int32_t *table, int64_t
   PLAN_CUDA(cudaGetLastError());
   P->nnz_covered = (int64_t)stat[0]; P->max_row = (int64_t)stat[1]; P->nnz_lo = (int64_t)stat[2]; P->nnz_hi = (int64_t)stat[3];
   if (!(bad & 3) && P->max_row <= MAXROW) {
-    const int chw = ACCW - (int)P->max_row;        // a tile = rows starting inside one window of chw CSR entries: span <= ACCW
-    P->ntiles = (P->nnz_hi - P->nnz_lo + chw - 1) / chw;
+    // Tiles: greedy over the plan rows, on the host (a sequential scan of 8 bytes per row; symbolic phase).  A tile is closed
+    // when its CSR span would exceed the warp's window, at TILE_MAXROWS rows, or at TILE_MAXPAIRS pairs -- so tiles of long
+    // rows (24 pairs on a P2 vertex row) hold 32 rows, one per lane, and tiles of short rows two per lane.
+    std::vector<int64_t> h_span(2 * nrows), h_pairptr(nrows + 1);
+    {
+      int64_t *d_span = nullptr;
+      PLAN_CUDA(cudaMalloc(&d_span, 2 * nrows * sizeof(int64_t)));
+      k_row_spans<<<(unsigned)((nrows + 255) / 256), 256, 0, st>>>(nrows, P->rows, rowptr, d_span);
+      cudaError_t ce = cudaMemcpyAsync(h_span.data(), d_span, 2 * nrows * sizeof(int64_t), cudaMemcpyDeviceToHost, st);
+      if (ce == cudaSuccess) ce = cudaMemcpyAsync(h_pairptr.data(), P->pairptr, (nrows + 1) * sizeof(int64_t), cudaMemcpyDeviceToHost, st);
+      if (ce == cudaSuccess) ce = cudaStreamSynchronize(st);
+      cudaFree(d_span);
+      PLAN_CUDA(ce);
+    }
+    std::vector<int32_t> h_tile_q;
+    std::vector<RowRec> h_rowrec(nrows);
+    h_tile_q.reserve(nrows / 16 + 2);
+    int64_t q0 = 0;
+    h_tile_q.push_back(0);
+    for (int64_t q = 0; q < nrows; q++) {
+      const int64_t np = h_pairptr[q + 1] - h_pairptr[q];
+      if (np > 65535) bad |= 4;
+      if (q > q0 && (h_span[2 * q + 1] - h_span[2 * q0] > ACCW || q - q0 >= TILE_MAXROWS ||
+                     h_pairptr[q + 1] - h_pairptr[q0] > TILE_MAXPAIRS)) {
+        q0 = q;
+        h_tile_q.push_back((int32_t)q);
+      }
+      RowRec r;
+      r.p0 = (uint32_t)h_pairptr[q]; r.np = (uint16_t)np; r.off = (uint16_t)(h_span[2 * q] - h_span[2 * q0]);
+      h_rowrec[q] = r;
+    }
+    h_tile_q.push_back((int32_t)nrows);
+    P->ntiles = (int64_t)h_tile_q.size() - 1;
     PLAN_CUDA(cudaMalloc(&P->tile_q, (P->ntiles + 1) * sizeof(int32_t)));
     PLAN_CUDA(cudaMalloc(&P->rowrec, nrows * sizeof(RowRec)));
-    k_plan_tiles<<<(unsigned)((P->ntiles + 1 + 255) / 256), 256, 0, st>>>(P->ntiles, nrows, P->nnz_lo, chw, P->rows, rowptr, P->tile_q);
-    k_plan_rowrec<<<(unsigned)((nrows + 255) / 256), 256, 0, st>>>(nrows, P->nnz_lo, chw, P->rows, P->pairptr, rowptr, P->tile_q, P->rowrec, d_bad);
+    PLAN_CUDA(cudaMemcpyAsync(P->tile_q, h_tile_q.data(), (P->ntiles + 1) * sizeof(int32_t), cudaMemcpyHostToDevice, st));
+    PLAN_CUDA(cudaMemcpyAsync(P->rowrec, h_rowrec.data(), nrows * sizeof(RowRec), cudaMemcpyHostToDevice, st));
+    PLAN_CUDA(cudaStreamSynchronize(st));          // the host vectors go out of use only after the copies
+    g_launches.fetch_add(1);
     // tile processing order
     uint32_t *ck = nullptr, *ck2 = nullptr;
     int32_t *ci2 = nullptr, *order = nullptr;

@@ -33,6 +33,14 @@ struct ngsx_rowplan {
 
 namespace ngsx {
 
+// reference tables of the constant-rule path (k_ref_tables -> k_rows):  [0, nd^2) mass table Tm[i][j];  then per shape i the
+// gradient-moment block cM[i][a][n] (dim x (dim+1) doubles) at stride CS -- CS/2 is odd so that the 16-byte shared-memory
+// slots of different i fall into different bank groups
+template <int DIM> struct RefTab {
+  static constexpr int CS = DIM == 3 ? 14 : 6;
+  static __host__ __device__ constexpr int cm_offset(int ne) { return (ne + 1) & ~1; }    // 16-byte aligned start of the cM blocks
+};
+
 // geometry-factor record (8 doubles per list entry): g[0..5] = |det J| c_stiff (J^-1 J^-T) upper triangle, g[6] = |det J| c_mass,
 // g[7] = code as int64: -1 no contribution, 0 constant-rule element, s+1 = row s of cutmats
 constexpr int GSTRIDE = 8;
