@@ -18,11 +18,27 @@
 
 namespace ngsx {
 
-constexpr int RW = 4;             // warps per CTA of the row kernel
-constexpr int MAXROW = 256;       // longest supported CSR row (column positions are bytes)
-constexpr int ACCW = 2176;        // doubles of shared memory per warp: the CSR span of one tile (17 KB)
-constexpr int TILE_MAXROWS = 64;  // rows per tile (2 per lane) ...
-constexpr int TILE_MAXPAIRS = 768;// ... and (row, element) pairs per tile (24 per lane)
+// tuning knobs (overridable with -D for sweeps; the defaults are the measured best on B200 at config 2)
+#ifndef NGSX_RW
+#define NGSX_RW 4
+#endif
+#ifndef NGSX_ACCW
+#define NGSX_ACCW 1400
+#endif
+#ifndef NGSX_TILE_MAXROWS
+#define NGSX_TILE_MAXROWS 64
+#endif
+#ifndef NGSX_MINBLOCKS
+#define NGSX_MINBLOCKS 4
+#endif
+#ifndef NGSX_TILE_MAXPAIRS
+#define NGSX_TILE_MAXPAIRS 768
+#endif
+constexpr int RW = NGSX_RW;                        // warps per CTA of the row kernel
+constexpr int MAXROW = 256;                        // longest supported CSR row (column positions are bytes)
+constexpr int ACCW = NGSX_ACCW;                    // doubles of shared memory per warp: the CSR span of one tile (11 KB -> 4 CTAs = 16 warps per SM)
+constexpr int TILE_MAXROWS = NGSX_TILE_MAXROWS;    // rows per tile (2 per lane) ...
+constexpr int TILE_MAXPAIRS = NGSX_TILE_MAXPAIRS;  // ... and (row, element) pairs per tile (24 per lane)
 
 // ---- plan construction --------------------------------------------------------------------------------------------
 // key = (row, local row i, list index k): the pairs of a row are walked grouped by i, so that the lanes of a warp mostly
@@ -321,7 +337,7 @@ __device__ __forceinline__ void lane_start(const RowArgs &A, int64_t tt, int lan
 }
 
 template <int DIM, int ORDER>
-__global__ void __launch_bounds__(RW * 32) k_rows(RowArgs A) {
+__global__ void __launch_bounds__(RW * 32, NGSX_MINBLOCKS) k_rows(RowArgs A) {
   constexpr int ND = H1<DIM, ORDER>::ND, NE = ND * ND, CS = RefTab<DIM>::CS, CMO = RefTab<DIM>::cm_offset(NE), NTAB = CMO + ND * CS;
   extern __shared__ __align__(16) double smem_rows[];
   double *tab = smem_rows;                                        // mass table [ND][ND], then cM [ND][CS]
