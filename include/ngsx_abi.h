@@ -21,7 +21,10 @@
  *   ngsx_integrate            cutint/python_cutint.cpp:20-72        (IntegrateX)
  *   ngsx_facets_neighbor_types, ngsx_elements_with_neighbor_facets, ngsx_dofs_of_elements
  *                             xfem/cutinfo.cpp:191-304              (xfem/python_xfem.cpp:168-318)
- *   ngsx_facetpatch_elmat_h1  xfem/symboliccutbfi.cpp:1115-1411     (CalcFacetMatrix, xfem/symboliccutbfi.hpp:253-259)
+ *   ngsx_facetpatch_elmat_h1, ngsx_facetpatch_cmat_h1
+ *                             xfem/symboliccutbfi.cpp:1115-1411     (CalcFacetMatrix, xfem/symboliccutbfi.hpp:253-259)
+ *   ngsx_facetpatch_table_h1, ngsx_assemble_csr_rows_mats
+ *                             NGS/comp/bilinearform.cpp:1800-1853 (facet loop: compressed dofs + AddElementMatrix)
  *
  * Bit arrays are uint32 words, bit i of the array = word i/32, bit i%32: layout-compatible with netgen's
  * ngcore::BitArray (NG/libsrc/core/bitarray.hpp:150-155: byte i/8, mask 1<<(i%8)) on little-endian hosts.
@@ -168,8 +171,8 @@ int ngsx_assemble_vec_h1(const ngsx_mesh *mesh, const double *lset_v, int fe_ord
  * contributions of one entry are summed in list order by a single warp, so the values are bitwise reproducible and no
  * floating-point atomic is used.  Multi-GPU: a plan restricted to rows [row_lo, row_hi) makes the rank the owner of those
  * rows -- it recomputes the halo elements listed in `table` instead of exchanging interface rows.
- * table [nlist][nd]: dofs of list entry k (list order fixes the summation order); rows longer than 256 entries are
- * NGSX_ERR_UNSUPPORTED (use the coloured path). */
+ * table [nlist][nd]: dofs of list entry k (list order fixes the summation order), nd <= 27, the nd dofs of one entry
+ * distinct; rows longer than 256 entries are NGSX_ERR_UNSUPPORTED (use the coloured path). */
 typedef struct ngsx_rowplan ngsx_rowplan;   /* opaque, owns device buffers (pair descriptors, geometry factors, cut-element matrices) */
 int ngsx_rowplan_create(int64_t nlist, int32_t nd, const int32_t *table, int64_t ndof, const int64_t *rowptr, const int32_t *colidx,
                         int64_t row_lo, int64_t row_hi, ngsx_rowplan **out, void *stream);
@@ -183,6 +186,11 @@ int ngsx_rowplan_destroy(ngsx_rowplan *plan);
 int ngsx_assemble_csr_rows_h1(const ngsx_mesh *mesh, const double *lset_v, int fe_order, int dt, int intorder,
                               const ngsx_form_h1 *h_form, int64_t nlist, const int32_t *els, ngsx_rowplan *plan,
                               int accumulate, double *vals, int64_t *err, void *stream);
+
+/* General form of AddElementMatrix (NGS/linalg/sparsematrix_impl.hpp:63-103) over a plan: mats [nlist][nd][nd] row-major
+ * blocks of the plan's list entries (elements, or facet patches with their merged dof lists) are gathered row by row;
+ * accumulate as above.  nd in {3, 4, 5, 6, 9, 10, 14, 20}. */
+int ngsx_assemble_csr_rows_mats(ngsx_rowplan *plan, const double *mats, int accumulate, double *vals, void *stream);
 
 /* ---- Integrate ------------------------------------------------------------------------------------------------- */
 /* out[0] = sum_e sum_q |det J_e| w_q f(x_q) over the (dt, order) cut rule; fixed-shape tree reduction (bitwise
@@ -203,6 +211,16 @@ int ngsx_dofs_of_elements(int64_t n, int32_t nd, const int32_t *table, const uin
  * (py_tutorials/fictdom_ghostpen.py:105-107); patch_els [np][2]; elmats [np][2nd][2nd] over [dofs(el0) | dofs(el1)]. */
 int ngsx_facetpatch_elmat_h1(const ngsx_mesh *mesh, int fe_order, double coef, int hpow, int64_t npatch,
                              const int32_t *patch_els, double *elmats, void *stream);
+
+/* Merged patch blocks for the row gather (NGSolve's compressed_dnums / compressed_elmat, NGS/comp/bilinearform.cpp:1800-1853).
+ * ngsx_facetpatch_table_h1 (symbolic, synchronises): table [np][ndp] = dofs of element 0, then the dofs of element 1 that
+ * element 0 does not have; cidx [np][2 nd] = position of every local dof of [dofs(el0) | dofs(el1)] in that list.
+ * ndp = 2 nd - (dofs on the shared facet): 4 / 9 (trig P1 / P2), 5 / 14 (tet P1 / P2).
+ * ngsx_facetpatch_cmat_h1 (numeric): mats [np][ndp][ndp] = C em C^T of ngsx_facetpatch_elmat_h1, integrated in merged form. */
+int ngsx_facetpatch_table_h1(int64_t npatch, const int32_t *patch_els, int32_t nd, const int32_t *el2dof, int32_t ndp,
+                             int32_t *table, uint8_t *cidx, void *stream);
+int ngsx_facetpatch_cmat_h1(const ngsx_mesh *mesh, int fe_order, double coef, int hpow, int64_t npatch,
+                            const int32_t *patch_els, const uint8_t *cidx, int32_t ndp, double *mats, void *stream);
 
 #ifdef __cplusplus
 }

@@ -76,6 +76,9 @@ SIGNATURES = {
     "ngsx_elements_with_neighbor_facets": (c_int, [c_i64, c_void_p, c_void_p, c_i64, c_void_p, c_void_p]),
     "ngsx_dofs_of_elements": (c_int, [c_i64, c_i32, c_void_p, c_void_p, c_i64, c_void_p, c_void_p]),
     "ngsx_facetpatch_elmat_h1": (c_int, [ctypes.POINTER(Mesh), c_int, c_double, c_int, c_i64, c_void_p, c_void_p, c_void_p]),
+    "ngsx_assemble_csr_rows_mats": (c_int, [c_void_p, c_void_p, c_int, c_void_p, c_void_p]),
+    "ngsx_facetpatch_table_h1": (c_int, [c_i64, c_void_p, c_i32, c_void_p, c_i32, c_void_p, c_void_p, c_void_p]),
+    "ngsx_facetpatch_cmat_h1": (c_int, [ctypes.POINTER(Mesh), c_int, c_double, c_int, c_i64, c_void_p, c_void_p, c_i32, c_void_p, c_void_p]),
 }
 
 _LIB = None

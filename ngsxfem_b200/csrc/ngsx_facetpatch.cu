@@ -119,6 +119,132 @@ static int launch_fp(const ngsx_mesh &M, const DeviceData *dd, const double4 *ru
   return NGSX_OK;
 }
 
+// ---- merged ("compressed") patch blocks: the form the row gather consumes --------------------------------------------
+// NGSolve merges the dofs the two elements of a patch share before AddElementMatrix (compressed_dnums / compressed_elmat,
+// NGS/comp/bilinearform.cpp:1800-1853).  Here the merge happens before the quadrature: cidx[a] is the position of local
+// dof a of [dofs(el0) | dofs(el1)] in the merged list (dofs of el0, then the dofs of el1 not in el0), and the kernel
+// integrates the merged jump vector directly -- (2 nd - shared)^2 instead of (2 nd)^2 products per point.
+__global__ void __launch_bounds__(128) k_fp_table(int64_t npatch, const int32_t *__restrict__ patch_els, int nd, const int32_t *__restrict__ el2dof,
+                                                 int ndp, int32_t *__restrict__ table, uint8_t *__restrict__ cidx, int *__restrict__ bad) {
+  const int64_t k = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (k >= npatch) return;
+  const int32_t *d0 = el2dof + (int64_t)patch_els[2 * k] * nd, *d1 = el2dof + (int64_t)patch_els[2 * k + 1] * nd;
+  int32_t *t = table + k * ndp;
+  uint8_t *c = cidx + k * 2 * nd;
+  for (int a = 0; a < nd; a++) { if (a < ndp) t[a] = d0[a]; c[a] = (uint8_t)a; }
+  int n = nd;
+  for (int b = 0; b < nd; b++) {
+    const int32_t dof = d1[b];
+    int hit = -1;
+    for (int a = 0; a < nd; a++) if (d0[a] == dof) hit = a;
+    if (hit < 0) { hit = n; if (n < ndp) t[n] = dof; n++; }
+    c[nd + b] = (uint8_t)hit;
+  }
+  if (n != ndp) atomicOr(bad, 1);
+}
+
+template <int DIM, int ORDER>
+__global__ void __launch_bounds__(FP_WARPS * 32) k_facetpatch_c(ngsx_mesh M, const double4 *__restrict__ rule, int nr, double coef, int hpow,
+                                                               int64_t npatch, const int32_t *__restrict__ patch_els,
+                                                               const uint8_t *__restrict__ cidx, double *__restrict__ mats) {
+  constexpr int ND = H1<DIM, ORDER>::ND, NFD = DIM == 2 ? (ORDER == 1 ? 2 : 3) : (ORDER == 1 ? 3 : 6);   // dofs on the shared facet
+  constexpr int NP = 2 * ND - NFD, NE = NP * NP, T = (NE + 31) / 32;
+  extern __shared__ __align__(16) unsigned char smem_raw[];
+  double4 *srule = reinterpret_cast<double4 *>(smem_raw);
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  double *stage = reinterpret_cast<double *>(smem_raw + (size_t)nr * 32) + warp * (32 * NP + 32);
+  double *facq = stage + 32 * NP;
+  for (int i = threadIdx.x; i < nr; i += blockDim.x) srule[i] = rule[i];
+  __syncthreads();
+  const int64_t nwarps = (int64_t)gridDim.x * FP_WARPS;
+  for (int64_t k = (int64_t)blockIdx.x * FP_WARPS + warp; k < npatch; k += nwarps) {
+    double p[2][DIM + 1][DIM];
+    ElGeom<DIM> G[2];
+    double hfac[2];
+    for (int s = 0; s < 2; s++) {
+      load_el_geo<DIM>(M, patch_els[2 * k + s], p[s]);
+      element_geometry<DIM>(p[s], G[s]);
+    }
+    {
+      const double m0 = fabs(G[0].det);
+      const double h = DIM == 2 ? sqrt(m0) : cbrt(m0);
+      const double c = coef * ipow(h, hpow);
+      hfac[0] = c * m0;
+      hfac[1] = c * fabs(G[1].det);
+    }
+    const uint8_t *ci = cidx + k * 2 * ND;
+    double acc[T];
+#pragma unroll
+    for (int t = 0; t < T; t++) acc[t] = 0.0;
+    const int ntot = 2 * nr;
+    for (int q0 = 0; q0 < ntot; q0 += 32) {
+      const int nq = min(32, ntot - q0);
+      if (lane < nq) {
+        const int q = q0 + lane, side = q >= nr ? 1 : 0;
+        const double4 r = srule[q - side * nr];
+        double lam[4] = {r.x, r.y, r.z, 0.0}, last = 1.0;
+#pragma unroll
+        for (int kk = 0; kk < DIM; kk++) last -= lam[kk];
+        lam[DIM] = last;
+        double x[DIM];
+#pragma unroll
+        for (int d = 0; d < DIM; d++) {
+          double v = 0.0;
+#pragma unroll
+          for (int kk = 0; kk <= DIM; kk++) v += lam[kk] * p[side][kk][d];
+          x[d] = v;
+        }
+        double lo[4] = {0.0, 0.0, 0.0, 0.0}, lasto = 1.0;
+#pragma unroll
+        for (int kk = 0; kk < DIM; kk++) {
+          double v = 0.0;
+#pragma unroll
+          for (int d = 0; d < DIM; d++) v += G[1 - side].Jinv[kk][d] * (x[d] - p[1 - side][DIM][d]);
+          lo[kk] = v; lasto -= v;
+        }
+        lo[DIM] = lasto;
+        double *jc = stage + lane * NP;
+        for (int c = 0; c < NP; c++) jc[c] = 0.0;
+        for (int i = 0; i < ND; i++) {
+          jc[ci[side * ND + i]] += h1_shape<DIM, ORDER>(i, lam);
+          jc[ci[(1 - side) * ND + i]] -= h1_shape<DIM, ORDER>(i, lo);
+        }
+        facq[lane] = hfac[side] * r.w;
+      }
+      __syncwarp();
+      for (int q = 0; q < nq; q++) {
+        const double f = facq[q];
+#pragma unroll
+        for (int t = 0; t < T; t++) {
+          const int idx = lane + 32 * t;
+          if (idx < NE) acc[t] += f * stage[q * NP + idx / NP] * stage[q * NP + idx % NP];
+        }
+      }
+      __syncwarp();
+    }
+#pragma unroll
+    for (int t = 0; t < T; t++) {
+      const int idx = lane + 32 * t;
+      if (idx < NE) mats[k * NE + idx] = acc[t];
+    }
+  }
+}
+
+template <int DIM, int ORDER>
+static int launch_fpc(const ngsx_mesh &M, const DeviceData *dd, const double4 *rule, int nr, double coef, int hpow, int64_t np,
+                      const int32_t *patch_els, const uint8_t *cidx, int ndp, double *mats, cudaStream_t st) {
+  constexpr int ND = H1<DIM, ORDER>::ND, NFD = DIM == 2 ? (ORDER == 1 ? 2 : 3) : (ORDER == 1 ? 3 : 6), NP = 2 * ND - NFD;
+  if (ndp != NP) { set_error("facetpatch_cmat: ndp does not match the merged dof count of this element type"); return NGSX_ERR_ARG; }
+  size_t smem = (size_t)nr * 32 + (size_t)FP_WARPS * (32 * NP + 32) * 8;
+  auto kern = k_facetpatch_c<DIM, ORDER>;
+  NGSX_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  int64_t need = (np + FP_WARPS - 1) / FP_WARPS;
+  unsigned grid = (unsigned)std::max<int64_t>(1, std::min<int64_t>(need, (int64_t)dd->sm_count * 8));
+  kern<<<grid, FP_WARPS * 32, smem, st>>>(M, rule, nr, coef, hpow, np, patch_els, cidx, mats);
+  NGSX_LAUNCH_CHECK();
+  return NGSX_OK;
+}
+
 }  // namespace ngsx
 
 using namespace ngsx;
@@ -139,6 +265,46 @@ extern "C" int ngsx_facetpatch_elmat_h1(const ngsx_mesh *mesh, int fe_order, dou
     case 22: return launch_fp<2, 2>(*mesh, dd, rule, nr, coef, hpow, npatch, patch_els, elmats, st);
     case 31: return launch_fp<3, 1>(*mesh, dd, rule, nr, coef, hpow, npatch, patch_els, elmats, st);
     case 32: return launch_fp<3, 2>(*mesh, dd, rule, nr, coef, hpow, npatch, patch_els, elmats, st);
+  }
+  return NGSX_ERR_UNSUPPORTED;
+}
+
+extern "C" int ngsx_facetpatch_table_h1(int64_t npatch, const int32_t *patch_els, int32_t nd, const int32_t *el2dof, int32_t ndp,
+                                        int32_t *table, uint8_t *cidx, void *stream) {
+  NGSX_REQUIRE(npatch >= 0 && nd > 0 && nd <= 64 && ndp >= nd && ndp <= 2 * nd, "facetpatch_table: bad arguments");
+  if (npatch == 0) return NGSX_OK;
+  NGSX_REQUIRE(patch_els && el2dof && table && cidx, "facetpatch_table: NULL array");
+  cudaStream_t st = as_stream(stream);
+  int *bad = nullptr;
+  NGSX_CUDA(cudaMallocAsync(&bad, sizeof(int), st));
+  NGSX_CUDA(cudaMemsetAsync(bad, 0, sizeof(int), st));
+  k_fp_table<<<(unsigned)((npatch + 127) / 128), 128, 0, st>>>(npatch, patch_els, nd, el2dof, ndp, table, cidx, bad);
+  g_launches.fetch_add(1);
+  int h_bad = 0;
+  cudaError_t e = cudaMemcpyAsync(&h_bad, bad, sizeof(int), cudaMemcpyDeviceToHost, st);
+  if (e == cudaSuccess) e = cudaStreamSynchronize(st);
+  cudaFreeAsync(bad, st);
+  NGSX_CUDA(e);
+  if (h_bad) { set_error("facetpatch_table: a patch does not share exactly 2 nd - ndp dofs (non-conforming space or wrong ndp)"); return NGSX_ERR_ARG; }
+  return NGSX_OK;
+}
+
+extern "C" int ngsx_facetpatch_cmat_h1(const ngsx_mesh *mesh, int fe_order, double coef, int hpow, int64_t npatch,
+                                       const int32_t *patch_els, const uint8_t *cidx, int32_t ndp, double *mats, void *stream) {
+  NGSX_REQUIRE(mesh && (mesh->dim == 2 || mesh->dim == 3) && mesh->vert && mesh->el2v, "facetpatch_cmat: bad mesh");
+  NGSX_REQUIRE(npatch >= 0 && (npatch == 0 || (patch_els && cidx && mats)), "facetpatch_cmat: bad arguments");
+  if (fe_order < 1 || fe_order > 2) { set_error("facetpatch_cmat: H1 order outside the CUDA path (1, 2)"); return NGSX_ERR_UNSUPPORTED; }
+  const DeviceData *dd = device_data();
+  if (!dd) return NGSX_ERR_CUDA;
+  const double4 *rule; int nr;
+  if (!rule_lookup(dd, mesh->dim, 2 * fe_order, &rule, &nr)) { set_error("facetpatch_cmat: rule not tabulated"); return NGSX_ERR_UNSUPPORTED; }
+  if (npatch == 0) return NGSX_OK;
+  cudaStream_t st = as_stream(stream);
+  switch (mesh->dim * 10 + fe_order) {
+    case 21: return launch_fpc<2, 1>(*mesh, dd, rule, nr, coef, hpow, npatch, patch_els, cidx, ndp, mats, st);
+    case 22: return launch_fpc<2, 2>(*mesh, dd, rule, nr, coef, hpow, npatch, patch_els, cidx, ndp, mats, st);
+    case 31: return launch_fpc<3, 1>(*mesh, dd, rule, nr, coef, hpow, npatch, patch_els, cidx, ndp, mats, st);
+    case 32: return launch_fpc<3, 2>(*mesh, dd, rule, nr, coef, hpow, npatch, patch_els, cidx, ndp, mats, st);
   }
   return NGSX_ERR_UNSUPPORTED;
 }

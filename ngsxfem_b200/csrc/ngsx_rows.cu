@@ -18,28 +18,6 @@
 
 namespace ngsx {
 
-// tuning knobs (overridable with -D for sweeps; the defaults are the measured best on B200 at config 2)
-#ifndef NGSX_RW
-#define NGSX_RW 4
-#endif
-#ifndef NGSX_ACCW
-#define NGSX_ACCW 1400
-#endif
-#ifndef NGSX_TILE_MAXROWS
-#define NGSX_TILE_MAXROWS 64
-#endif
-#ifndef NGSX_MINBLOCKS
-#define NGSX_MINBLOCKS 4
-#endif
-#ifndef NGSX_TILE_MAXPAIRS
-#define NGSX_TILE_MAXPAIRS 768
-#endif
-constexpr int RW = NGSX_RW;                        // warps per CTA of the row kernel
-constexpr int MAXROW = 256;                        // longest supported CSR row (column positions are bytes)
-constexpr int ACCW = NGSX_ACCW;                    // doubles of shared memory per warp: the CSR span of one tile (11 KB -> 4 CTAs = 16 warps per SM)
-constexpr int TILE_MAXROWS = NGSX_TILE_MAXROWS;    // rows per tile (2 per lane) ...
-constexpr int TILE_MAXPAIRS = NGSX_TILE_MAXPAIRS;  // ... and (row, element) pairs per tile (24 per lane)
-
 // ---- plan construction --------------------------------------------------------------------------------------------
 // key = (row, local row i, list index k): the pairs of a row are walked grouped by i, so that the lanes of a warp mostly
 // read the same rows of the reference tables in the same step (shared-memory broadcast instead of distinct wavefronts)
@@ -160,13 +138,6 @@ __global__ void __launch_bounds__(256) k_tile_tables(int64_t nact, const int32_t
     if (pairptr[mid] < target) lo = mid + 1; else hi = mid;
   }
   split[t] = lo;
-}
-
-__device__ __forceinline__ RowRec ld_rowrec(const RowRec *p) {
-  const uint2 u = __ldg(reinterpret_cast<const uint2 *>(p));
-  RowRec r;
-  r.p0 = u.x; r.np = (uint16_t)(u.y & 0xffffu); r.off = (uint16_t)(u.y >> 16);
-  return r;
 }
 
 // byte 5 + j of a descriptor = position of local column j in the row
@@ -426,6 +397,7 @@ int rows_scratch(ngsx_rowplan *P, int npairtab) {
 
 int launch_rows(const ngsx_rowplan *P, int npairtab, int accumulate, double *vals, int sm_count, cudaStream_t st) {
   if (P->nrows == 0) return NGSX_OK;
+  if (P->ds != 16) { set_error("row gather: this plan was built for merged facet-patch dof lists (use ngsx_assemble_csr_rows_mats)"); return NGSX_ERR_ARG; }
   RowArgs A{P->ntiles_active, P->tile_info, P->tile_split, P->rowrec, reinterpret_cast<const uint4 *>(P->desc), P->G, P->cutmats, P->tab,
             vals, accumulate};
   switch (P->nd * 10 + npairtab) {
@@ -462,14 +434,14 @@ int ngsx_rowplan_info(const ngsx_rowplan *P, int64_t *h_info) {
 
 int ngsx_rowplan_create(int64_t nlist, int32_t nd, const int32_t *table, int64_t ndof, const int64_t *rowptr, const int32_t *colidx,
                         int64_t row_lo, int64_t row_hi, ngsx_rowplan **out, void *stream) {
-  NGSX_REQUIRE(out && nlist >= 0 && nd > 0 && nd <= 11 && ndof >= 0 && ndof < (1LL << 31) && rowptr, "rowplan_create: bad arguments");
+  NGSX_REQUIRE(out && nlist >= 0 && nd > 0 && nd <= 27 && ndof >= 0 && ndof < (1LL << 31) && rowptr, "rowplan_create: bad arguments");
   NGSX_REQUIRE(nlist == 0 || (table && colidx), "rowplan_create: table / colidx are NULL");
   NGSX_REQUIRE(nlist * nd < (1LL << 32), "rowplan_create: more than 2^32 (element, dof) pairs");
   cudaStream_t st = as_stream(stream);
   if (row_hi < 0 || row_hi > ndof) row_hi = ndof;
   if (row_lo < 0) row_lo = 0;
   ngsx_rowplan *P = new ngsx_rowplan();
-  P->nlist = nlist; P->nd = nd; P->ndof = ndof; P->ds = 16; P->rowptr = rowptr;
+  P->nlist = nlist; P->nd = nd; P->ndof = ndof; P->ds = nd <= 11 ? 16 : 32; P->rowptr = rowptr;
   *out = P;
   const int64_t nall = nlist * nd;
   if (nall == 0 || row_hi <= row_lo) return NGSX_OK;

@@ -6,7 +6,8 @@
 // One (row, element) pair descriptor, 16 bytes (one LDG.128):
 //   int32 k        list index of the element
 //   uint8 i        local row (the dof of the row inside element k)
-//   uint8 pos[nd]  position of local column j inside the CSR row (nd <= 11)
+//   uint8 pos[nd]  position of local column j inside the CSR row (nd <= 11; 32-byte descriptors for 11 < nd <= 27:
+//                  the merged dof lists of facet patches)
 namespace ngsx {
 struct RowRec { uint32_t p0; uint16_t np; uint16_t off; };   // first pair, number of pairs, offset of the row inside its tile
 struct TileInfo { int64_t z0; int32_t zlen; int32_t pad; };  // CSR span of a tile
@@ -32,6 +33,35 @@ struct ngsx_rowplan {
 };
 
 namespace ngsx {
+
+// tuning knobs (overridable with -D for sweeps; the defaults are the measured best on B200 at config 2)
+#ifndef NGSX_RW
+#define NGSX_RW 4
+#endif
+#ifndef NGSX_ACCW
+#define NGSX_ACCW 1400
+#endif
+#ifndef NGSX_TILE_MAXROWS
+#define NGSX_TILE_MAXROWS 64
+#endif
+#ifndef NGSX_MINBLOCKS
+#define NGSX_MINBLOCKS 4
+#endif
+#ifndef NGSX_TILE_MAXPAIRS
+#define NGSX_TILE_MAXPAIRS 768
+#endif
+constexpr int RW = NGSX_RW;                        // warps per CTA of the row kernel
+constexpr int MAXROW = 256;                        // longest supported CSR row (column positions are bytes)
+constexpr int ACCW = NGSX_ACCW;                    // doubles of shared memory per warp: the CSR span of one tile (11 KB -> 4 CTAs = 16 warps per SM)
+constexpr int TILE_MAXROWS = NGSX_TILE_MAXROWS;    // rows per tile (2 per lane) ...
+constexpr int TILE_MAXPAIRS = NGSX_TILE_MAXPAIRS;  // ... and (row, element) pairs per tile (24 per lane)
+
+__device__ __forceinline__ RowRec ld_rowrec(const RowRec *p) {
+  const uint2 u = __ldg(reinterpret_cast<const uint2 *>(p));
+  RowRec r;
+  r.p0 = u.x; r.np = (uint16_t)(u.y & 0xffffu); r.off = (uint16_t)(u.y >> 16);
+  return r;
+}
 
 // reference tables of the constant-rule path (k_ref_tables -> k_rows):  [0, nd^2) mass table Tm[i][j];  then per shape i the
 // gradient-moment block cM[i][a][n] (dim x (dim+1) doubles) at stride CS -- CS/2 is odd so that the 16-byte shared-memory

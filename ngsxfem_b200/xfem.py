@@ -486,6 +486,9 @@ class BilinearForm:
         return plan
 
     def _facetpatch_plan(self, integ: SymbolicFacetPatchBFI):
+        """symbolic phase of the ghost-penalty operator (NGS/comp/bilinearform.cpp:1800-1853): patches = inner facets (restricted
+        by definedonelements, which is a FACET BitArray for this integrator, xfem/python_xfem.cpp:534-606), merged dof list per
+        patch (ngsx_facetpatch_table_h1) and an owner-computes row plan over it"""
         fes, L = self.space, _lib_()
         mesh = fes.mesh
         _, f2e = mesh.facets()
@@ -494,20 +497,21 @@ class BilinearForm:
             inner = inner & integ.definedonelements.to_bool()
         fac = torch.nonzero(inner).reshape(-1)
         pe = f2e[fac].contiguous()                                     # [np][2] int32, element 0 = lower number
-        tab = torch.cat([fes.el2dof[pe[:, 0].long()], fes.el2dof[pe[:, 1].long()]], dim=1).contiguous()
-        # compressed dof list per patch (NGS/comp/bilinearform.cpp:1800-1853): duplicates -> first occurrence, rest -1
-        n2 = tab.shape[1]
-        eq = tab[:, :, None] == tab[:, None, :]
-        first = torch.argmax(eq.int(), dim=2)                          # first index holding the same dof
-        rep = first.to(torch.int32).contiguous()
-        perm, cptr = color_list(tab, fes.ndof, 1)
-        pe_s, tab_s, rep_s = pe[perm].contiguous(), tab[perm].contiguous(), rep[perm].contiguous()
-        slots = torch.empty((pe_s.shape[0], n2 * n2), dtype=torch.int32, device=mesh.device)
-        check(L.ngsx_slot_map(pe_s.shape[0], n2, _ptr(tab_s), _ptr(self.mat.rowptr), _ptr(self.mat.colidx), _ptr(slots), _stream()))
-        if pe_s.shape[0] and int(slots.min().item()) < 0:
-            raise NgsxError(-1, "facet-patch coupling missing from the sparsity pattern (dgjumps=True / facet_restriction needed)")
-        plan = _Plan(pe_s, tab_s, cptr, 1, slots)
-        plan.rep = rep_s
+        npatch = pe.shape[0]
+        nfd = {(2, 1): 2, (2, 2): 3, (3, 1): 3, (3, 2): 6}[(mesh.dim, fes.order)]          # dofs on the shared facet
+        ndp = 2 * fes.nd - nfd
+        table = torch.empty((npatch, ndp), dtype=torch.int32, device=mesh.device)
+        cidx = torch.empty((npatch, 2 * fes.nd), dtype=torch.uint8, device=mesh.device)
+        check(L.ngsx_facetpatch_table_h1(npatch, _ptr(pe), fes.nd, _ptr(fes.el2dof), ndp, _ptr(table), _ptr(cidx), _stream()))
+        h = ctypes.c_void_p()
+        lo, hi = self.row_range if self.row_range is not None else (0, fes.ndof)
+        check(L.ngsx_rowplan_create(npatch, ndp, _ptr(table), fes.ndof, _ptr(self.mat.rowptr), _ptr(self.mat.colidx),
+                                    lo, hi, ctypes.byref(h), _stream()))
+        info = (ctypes.c_int64 * 6)()
+        check(L.ngsx_rowplan_info(h, info))
+        plan = _RowPlan(pe, table, h, tuple(info))
+        plan.cidx, plan.ndp = cidx, ndp
+        plan.mats = torch.empty((npatch, ndp * ndp), dtype=torch.float64, device=mesh.device)
         return plan
 
     def Assemble(self, reallocate: bool = False):
@@ -520,7 +524,7 @@ class BilinearForm:
         plans = [self._plan_for(k, integ) for k, integ in enumerate(self.integrators)]
         # a single row plan that covers every stored entry overwrites its rows: no SetZero pass, each value written once
         # (with a row range: the rank's rows are one contiguous CSR span, the other rows belong to other ranks and stay untouched)
-        overwrite = len(plans) == 1 and isinstance(plans[0], _RowPlan) and \
+        overwrite = len(plans) == 1 and isinstance(self.integrators[0], SymbolicCutBFI) and isinstance(plans[0], _RowPlan) and \
             plans[0].nnz_covered == (self.mat.nnz if self.row_range is None else plans[0].nnz_hi - plans[0].nnz_lo)
         if not overwrite:
             self.mat.vals.zero_()
@@ -529,7 +533,9 @@ class BilinearForm:
         mesh_c = ctypes.byref(fes.mesh.c_struct())
         for k, integ in enumerate(self.integrators):
             plan = plans[k]
-            if isinstance(plan, _RowPlan):
+            if isinstance(integ, SymbolicFacetPatchBFI):
+                self._assemble_facetpatch(integ, plan)
+            elif isinstance(plan, _RowPlan):
                 lv = _lset_vec(integ.lset)
                 check(L.ngsx_assemble_csr_rows_h1(mesh_c, _ptr(lv), fes.order, integ.dt, integ.intorder(fes.order), ctypes.byref(integ.form),
                                                   plan.els.numel(), _ptr(plan.els), plan.handle, 0 if overwrite else 1,
@@ -540,8 +546,6 @@ class BilinearForm:
                 check(L.ngsx_assemble_csr_h1(mesh_c, _ptr(lv), fes.order, integ.dt, integ.intorder(fes.order), ctypes.byref(integ.form),
                                              plan.els.numel(), _ptr(plan.els), _ptr(plan.slots), plan.ncolors, plan.h_color_ptr,
                                              plan.group, _ptr(self.mat.vals), _stream()))
-            else:
-                self._assemble_facetpatch(integ, plan)
         return self
 
     def check_degenerate(self):
@@ -556,29 +560,16 @@ class BilinearForm:
                                 "'You tried to cut a simplex with a plain geometry lset function'")
 
     def _assemble_facetpatch(self, integ, plan):
-        """patch matrices on the device (ngsx_facetpatch_elmat_h1), duplicate dofs merged like NGSolve's compressed_elmat,
-        then a deterministic index_add in patch order (host-orchestrated torch scatter: plumbing for the NEXT row f-1)."""
+        """numeric phase: merged patch blocks (ngsx_facetpatch_cmat_h1), then the owner-computes gather adds them to the rows
+        they touch (ngsx_assemble_csr_rows_mats) -- plan order, no atomics, bitwise reproducible"""
         L = _lib_()
         fes = self.space
         npatch = plan.els.shape[0]
         if npatch == 0:
             return
-        n2 = 2 * fes.nd
-        em = torch.empty((npatch, n2 * n2), dtype=torch.float64, device=fes.mesh.device)
-        check(L.ngsx_facetpatch_elmat_h1(ctypes.byref(fes.mesh.c_struct()), fes.order, integ.coef, integ.hpow, npatch,
-                                         _ptr(plan.els), _ptr(em), _stream()))
-        # merge duplicate dofs of the two halves (NGSolve's compressed_elmat): C[rep[i], i] = 1, em_c = C em C^T
-        rep = plan.rep.long()
-        C = torch.zeros((npatch, n2, n2), dtype=torch.float64, device=em.device)
-        C.scatter_(1, rep[:, None, :], 1.0)
-        em_c = torch.bmm(torch.bmm(C, em.view(npatch, n2, n2)), C.transpose(1, 2))
-        is_rep = rep == torch.arange(n2, device=em.device)[None, :]
-        keep = (is_rep[:, :, None] & is_rep[:, None, :]).reshape(npatch, -1)
-        for c in range(plan.ncolors):            # colour by colour: slots are unique inside a colour -> plain deterministic +=
-            a, b = plan.color_ptr[c], plan.color_ptr[c + 1]
-            k = keep[a:b].reshape(-1)
-            idx = plan.slots[a:b].reshape(-1)[k].long()
-            self.mat.vals[idx] += em_c[a:b].reshape(-1)[k]
+        check(L.ngsx_facetpatch_cmat_h1(ctypes.byref(fes.mesh.c_struct()), fes.order, integ.coef, integ.hpow, npatch,
+                                        _ptr(plan.els), _ptr(plan.cidx), plan.ndp, _ptr(plan.mats), _stream()))
+        check(L.ngsx_assemble_csr_rows_mats(plan.handle, _ptr(plan.mats), 1, _ptr(self.mat.vals), _stream()))
 
     def elmats(self, k: int = 0):
         """dense element matrices of integrator k for its active elements (the per-element view CalcElementMatrixAdd would serve)"""

@@ -319,6 +319,60 @@ def test_facet_marking_and_patches(X):
         assert diff <= 1e-11 * abs(A).max()
 
 
+@pytest.mark.parametrize("dim,fo", [(2, 1), (2, 2), (3, 1), (3, 2)])
+def test_ghost_penalty_row_gather(X, dim, fo):
+    """f-1: fictitious-domain operator = NEG stiffness + ghost-penalty facet patches (py_tutorials/fictdom_ghostpen.py:86-107),
+    both through the owner-computes row gather; merged patch blocks vs C em C^T of the oracle's CalcFacetMatrix restatement."""
+    from oracle import orc
+    import scipy.sparse as sp
+    if dim == 2:
+        mesh = X.ngs.Mesh(X.meshes.MakeStructured2DMesh(10, lo=(-1, -1), hi=(1, 1)))
+        lset = X.ngs.RingLevelset((0, 0), 0.25, 0.75)
+    else:
+        mesh = X.ngs.Mesh(X.meshes.MakeStructured3DMesh(5))
+        lset = X.ngs.SphereLevelset((0.5, 0.5, 0.5), 0.35)
+    gf = X.ngs.GridFunction(X.ngs.H1(mesh, order=1))
+    X.xfem.InterpolateToP1(lset, gf)
+    ci = X.xfem.CutInfo(mesh, gf)
+    hasneg, hasif = ci.GetElementsOfType(X.xfem.HASNEG), ci.GetElementsOfType(IF)
+    ba = X.xfem.GetFacetsWithNeighborTypes(mesh, a=hasneg, b=hasif)
+    Vh = X.ngs.H1(mesh, order=fo, dgjumps=True)
+    u, v = Vh.TnT()
+    h = X.ngs.specialcf.mesh_size
+    a = X.xfem.RestrictedBilinearForm(Vh, element_restriction=hasneg, facet_restriction=ba)
+    a += X.xfem.SymbolicBFI(levelset_domain={"levelset": gf, "domain_type": NEG}, form=X.ngs.grad(u) * X.ngs.grad(v), definedonelements=hasneg)
+    a += X.xfem.SymbolicFacetPatchBFI(form=0.1 * 1.0 / h * 1.0 / h * (u - u.Other()) * (v - v.Other()), skeleton=False, definedonelements=ba)
+    a.Assemble()
+    first = a.mat.vals.clone()
+    a.mat.vals.fill_(float("nan"))
+    a.Assemble()
+    assert torch.equal(first, a.mat.vals)                                   # bitwise reproducible
+    plan = a._plans[1]
+    el2v, vert, e2d, ls = mesh.el2v.cpu().numpy(), mesh.vert.cpu().numpy(), Vh.el2dof.cpu().numpy(), gf.vec.cpu().numpy()
+    # merged blocks vs the oracle
+    pe, tab, mats = plan.els.cpu().numpy(), plan.table.cpu().numpy(), plan.mats.cpu().numpy()
+    ndp = plan.ndp
+    assert len(pe) == int(np.count_nonzero(ba.to_bool().cpu().numpy() & (mesh.facets()[1][:, 1] >= 0).cpu().numpy()))
+    A = sp.lil_matrix((Vh.ndof, Vh.ndof))
+    for k, (e0, e1) in enumerate(pe):
+        _, em = orc.facetpatch_elmat_h1(dim, fo, el2v[e0], vert[el2v[e0]], el2v[e1], vert[el2v[e1]], 0.1, -2)
+        d = np.concatenate([e2d[e0], e2d[e1]])
+        assert len(set(tab[k])) == ndp and set(tab[k]) == set(d)
+        C = (tab[k][:, None] == d[None, :]).astype(float)
+        ref = C @ em @ C.T
+        assert np.abs(mats[k].reshape(ndp, ndp) - ref).max() <= 1e-12 * np.abs(em).max()
+        for i in range(len(d)):
+            for j in range(len(d)):
+                A[d[i], d[j]] += em[i, j]
+    els = np.nonzero(hasneg.to_bool().cpu().numpy())[0]
+    rowptr, colidx = a.mat.rowptr.cpu().numpy(), a.mat.colidx.cpu().numpy()
+    vol, _ = orc.assemble_csr(dim, el2v, vert, ls, fo, e2d, 0, 2 * fo - 2, 0.0, 1.0, np.array([0, len(els)], dtype=np.int64), els.astype(np.int32),
+                              rowptr, colidx, nthreads=1)
+    ref = sp.csr_matrix((vol, colidx, rowptr), shape=(Vh.ndof, Vh.ndof)) + A.tocsr()
+    diff = abs(a.mat.to_scipy() - ref).max()
+    assert diff <= 1e-11 * abs(ref).max()
+
+
 def test_unsupported_paths_raise(X):
     mesh = X.ngs.Mesh(X.meshes.MakeStructured2DMesh(2))
     gf = X.ngs.GridFunction(X.ngs.H1(mesh, order=1))
