@@ -148,7 +148,7 @@ __global__ void __launch_bounds__(FP_WARPS * 32) k_facetpatch_c(ngsx_mesh M, con
                                                                int64_t npatch, const int32_t *__restrict__ patch_els,
                                                                const uint8_t *__restrict__ cidx, double *__restrict__ mats) {
   constexpr int ND = H1<DIM, ORDER>::ND, NFD = DIM == 2 ? (ORDER == 1 ? 2 : 3) : (ORDER == 1 ? 3 : 6);   // dofs on the shared facet
-  constexpr int NP = 2 * ND - NFD, NE = NP * NP, T = (NE + 31) / 32;
+  constexpr int NP = 2 * ND - NFD, NE = NP * NP, NS = NP * (NP + 1) / 2, T = (NS + 31) / 32;   // symmetric: upper triangle only
   extern __shared__ __align__(16) unsigned char smem_raw[];
   double4 *srule = reinterpret_cast<double4 *>(smem_raw);
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -156,6 +156,14 @@ __global__ void __launch_bounds__(FP_WARPS * 32) k_facetpatch_c(ngsx_mesh M, con
   double *facq = stage + 32 * NP;
   for (int i = threadIdx.x; i < nr; i += blockDim.x) srule[i] = rule[i];
   __syncthreads();
+  int ei[T], ej[T];                                  // this lane's upper-triangle entries
+#pragma unroll
+  for (int t = 0; t < T; t++) {
+    int idx = lane + 32 * t, i = 0;
+    if (idx >= NS) idx = 0;
+    while (idx >= NP - i) { idx -= NP - i; i++; }
+    ei[t] = i; ej[t] = i + idx;
+  }
   const int64_t nwarps = (int64_t)gridDim.x * FP_WARPS;
   for (int64_t k = (int64_t)blockIdx.x * FP_WARPS + warp; k < npatch; k += nwarps) {
     double p[2][DIM + 1][DIM];
@@ -216,16 +224,17 @@ __global__ void __launch_bounds__(FP_WARPS * 32) k_facetpatch_c(ngsx_mesh M, con
         const double f = facq[q];
 #pragma unroll
         for (int t = 0; t < T; t++) {
-          const int idx = lane + 32 * t;
-          if (idx < NE) acc[t] += f * stage[q * NP + idx / NP] * stage[q * NP + idx % NP];
+          acc[t] += f * stage[q * NP + ei[t]] * stage[q * NP + ej[t]];
         }
       }
       __syncwarp();
     }
 #pragma unroll
     for (int t = 0; t < T; t++) {
-      const int idx = lane + 32 * t;
-      if (idx < NE) mats[k * NE + idx] = acc[t];
+      if (lane + 32 * t < NS) {
+        mats[k * NE + ei[t] * NP + ej[t]] = acc[t];
+        mats[k * NE + ej[t] * NP + ei[t]] = acc[t];
+      }
     }
   }
 }
