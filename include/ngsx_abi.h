@@ -23,6 +23,7 @@
  *                             xfem/cutinfo.cpp:191-304              (xfem/python_xfem.cpp:168-318)
  *   ngsx_facetpatch_elmat_h1, ngsx_facetpatch_cmat_h1
  *                             xfem/symboliccutbfi.cpp:1115-1411     (CalcFacetMatrix, xfem/symboliccutbfi.hpp:253-259)
+ *   ngsx_xfem_elmat_h1        xfem/xfemdiffops.cpp:8-66 + xfem/symboliccutbfi.cpp:73-315 (compound [Vh, XFESpace] element)
  *   ngsx_facetpatch_table_h1, ngsx_assemble_csr_rows_mats
  *                             NGS/comp/bilinearform.cpp:1800-1853 (facet loop: compressed dofs + AddElementMatrix)
  *
@@ -189,7 +190,7 @@ int ngsx_assemble_csr_rows_h1(const ngsx_mesh *mesh, const double *lset_v, int f
 
 /* General form of AddElementMatrix (NGS/linalg/sparsematrix_impl.hpp:63-103) over a plan: mats [nlist][nd][nd] row-major
  * blocks of the plan's list entries (elements, or facet patches with their merged dof lists) are gathered row by row;
- * accumulate as above.  nd in {3, 4, 5, 6, 9, 10, 14, 20}. */
+ * accumulate as above.  nd in {3, 4, 5, 6, 8, 9, 10, 12, 14, 20}. */
 int ngsx_assemble_csr_rows_mats(ngsx_rowplan *plan, const double *mats, int accumulate, double *vals, void *stream);
 
 /* ---- Integrate ------------------------------------------------------------------------------------------------- */
@@ -211,6 +212,27 @@ int ngsx_dofs_of_elements(int64_t n, int32_t nd, const int32_t *table, const uin
  * (py_tutorials/fictdom_ghostpen.py:105-107); patch_els [np][2]; elmats [np][2nd][2nd] over [dofs(el0) | dofs(el1)]. */
 int ngsx_facetpatch_elmat_h1(const ngsx_mesh *mesh, int fe_order, double coef, int hpow, int64_t npatch,
                              const int32_t *patch_els, double *elmats, void *stream);
+
+/* ---- (f-2) XFEM: compound space [Vh, XFESpace(Vh)] with sign-masked operators --------------------------------------
+ * One product term of a bilinear form on the compound space:
+ *     coef * h^hpow * kappa * (L_v v) (L_u u)
+ * kappa: 0 none, 1 CutRatioGF (cut ratio of the element, xfem/cutinfo.cpp:91), 2 one minus it;
+ * pair : 0 value*value, 1 (test value)*(trial dn), 2 (test dn)*(trial value), 3 dn*dn, 4 grad.grad,  dn = grad . n,
+ *        n = grad(lset_p1)/|grad(lset_p1)|;
+ * blk_u / blk_v: which dofs carry the trial / test factor: 0 the dofs of Vh (u_std, grad(u_std)), 1 x-dofs of sign NEG
+ *        (neg(u_x), neg_grad(u_x)), 2 x-dofs of sign POS (pos, pos_grad)  -- DiffOpX<D, RNEG/RPOS/RNEG_GRAD/RPOS_GRAD>,
+ *        xfem/xfemdiffops.cpp:30-60. */
+typedef struct ngsx_xterm {
+  double  coef;
+  int32_t hpow, kappa, pair, blk_u, blk_v, _pad;
+} ngsx_xterm;
+/* mats [nlist][2 nd][2 nd] row-major over [dofs of Vh | x-dofs] of each listed element (rows = test functions): the block
+ * CalcElementMatrixAdd (xfem/symboliccutbfi.cpp:73-315) produces on a CompoundFiniteElement(H1 element, XFiniteElement).
+ * xsign [nlist][nd] int8: XFESpace::domofdof (NEG/POS) of the x-dof over local dof i (xfem/xFESpace.cpp:346-366);
+ * ratio [ne]: cut ratios of ngsx_classify.  Elements whose (dt) rule is empty give a zero block. */
+int ngsx_xfem_elmat_h1(const ngsx_mesh *mesh, const double *lset_v, int fe_order, int dt, int intorder, int32_t nterms,
+                       const ngsx_xterm *h_terms, int64_t nlist, const int32_t *els, const int8_t *xsign, const double *ratio,
+                       double *mats, void *stream);
 
 /* Merged patch blocks for the row gather (NGSolve's compressed_dnums / compressed_elmat, NGS/comp/bilinearform.cpp:1800-1853).
  * ngsx_facetpatch_table_h1 (symbolic, synchronises): table [np][ndp] = dofs of element 0, then the dofs of element 1 that

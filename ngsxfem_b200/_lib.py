@@ -35,6 +35,10 @@ class FormH1(ctypes.Structure):
                 ("hpow_mass", c_i32), ("hpow_stiff", c_i32), ("hpow_nitsche", c_i32), ("_pad", c_i32)]
 
 
+class XTerm(ctypes.Structure):
+    _fields_ = [("coef", c_double), ("hpow", c_i32), ("kappa", c_i32), ("pair", c_i32), ("blk_u", c_i32), ("blk_v", c_i32), ("_pad", c_i32)]
+
+
 class Poly(ctypes.Structure):
     _fields_ = [("nterms", c_i32), ("_pad", c_i32), ("coef", c_double * POLY_MAXTERMS), ("ex", (c_i32 * 3) * POLY_MAXTERMS)]
 
@@ -76,6 +80,8 @@ SIGNATURES = {
     "ngsx_elements_with_neighbor_facets": (c_int, [c_i64, c_void_p, c_void_p, c_i64, c_void_p, c_void_p]),
     "ngsx_dofs_of_elements": (c_int, [c_i64, c_i32, c_void_p, c_void_p, c_i64, c_void_p, c_void_p]),
     "ngsx_facetpatch_elmat_h1": (c_int, [ctypes.POINTER(Mesh), c_int, c_double, c_int, c_i64, c_void_p, c_void_p, c_void_p]),
+    "ngsx_xfem_elmat_h1": (c_int, [ctypes.POINTER(Mesh), c_void_p, c_int, c_int, c_int, c_i32, ctypes.POINTER(XTerm), c_i64, c_void_p, c_void_p,
+                                   c_void_p, c_void_p, c_void_p]),
     "ngsx_assemble_csr_rows_mats": (c_int, [c_void_p, c_void_p, c_int, c_void_p, c_void_p]),
     "ngsx_facetpatch_table_h1": (c_int, [c_i64, c_void_p, c_i32, c_void_p, c_i32, c_void_p, c_void_p, c_void_p]),
     "ngsx_facetpatch_cmat_h1": (c_int, [ctypes.POINTER(Mesh), c_int, c_double, c_int, c_i64, c_void_p, c_void_p, c_i32, c_void_p, c_void_p]),

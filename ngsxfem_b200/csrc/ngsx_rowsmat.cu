@@ -149,11 +149,13 @@ extern "C" int ngsx_assemble_csr_rows_mats(ngsx_rowplan *plan, const double *mat
     case 4: return launch_rows_mats_t<4>(A, dd->sm_count, st);
     case 5: return launch_rows_mats_t<5>(A, dd->sm_count, st);
     case 6: return launch_rows_mats_t<6>(A, dd->sm_count, st);
+    case 8: return launch_rows_mats_t<8>(A, dd->sm_count, st);
     case 9: return launch_rows_mats_t<9>(A, dd->sm_count, st);
     case 10: return launch_rows_mats_t<10>(A, dd->sm_count, st);
+    case 12: return launch_rows_mats_t<12>(A, dd->sm_count, st);
     case 14: return launch_rows_mats_t<14>(A, dd->sm_count, st);
     case 20: return launch_rows_mats_t<20>(A, dd->sm_count, st);
   }
-  set_error("assemble_csr_rows_mats: unsupported block size (3, 4, 5, 6, 9, 10, 14, 20)");
+  set_error("assemble_csr_rows_mats: unsupported block size (3, 4, 5, 6, 8, 9, 10, 12, 14, 20)");
   return NGSX_ERR_UNSUPPORTED;
 }

@@ -18,7 +18,7 @@ namespace ngsx {
 
 constexpr int XW = 4;             // warps per CTA
 constexpr int XQ = 16;            // quadrature points staged per round
-constexpr int XMAXTERMS = 24;
+constexpr int XMAXTERMS = 32;
 
 struct XTermsDev {
   int n;
@@ -111,7 +111,7 @@ __global__ void __launch_bounds__(XW * 32) k_xfem(ngsx_mesh M, const double *__r
         for (int q0 = 0; q0 < nr; q0 += XQ) {
           const int nq = min(XQ, nr - q0);
           if (lane < nq) {
-            const double4 r = __ldg(rule + q0 + lane);
+            const double4 r = rule[q0 + lane];
             double xi[3] = {r.x, r.y, r.z};
             if (cut) simplex_point(E.npt, P, r, xi);
             double lam[4] = {xi[0], xi[1], xi[2], 0.0};
@@ -210,7 +210,7 @@ extern "C" int ngsx_xfem_elmat_h1(const ngsx_mesh *mesh, const double *lset_v, i
   NGSX_REQUIRE(mesh && (mesh->dim == 2 || mesh->dim == 3) && mesh->vert && mesh->el2v && lset_v, "xfem_elmat: bad mesh / level set");
   NGSX_REQUIRE(dt >= 0 && dt <= 2 && nlist >= 0 && nterms >= 0 && (nterms == 0 || h_terms), "xfem_elmat: bad arguments");
   NGSX_REQUIRE(nlist == 0 || (xsign && ratio && mats), "xfem_elmat: NULL array");
-  if (nterms > XMAXTERMS) { set_error("xfem_elmat: more than 24 product terms"); return NGSX_ERR_UNSUPPORTED; }
+  if (nterms > XMAXTERMS) { set_error("xfem_elmat: more than 32 product terms"); return NGSX_ERR_UNSUPPORTED; }
   if (fe_order < 1 || fe_order > 2) { set_error("xfem_elmat: H1 order outside the CUDA path (1, 2); no CPU fallback"); return NGSX_ERR_UNSUPPORTED; }
   const DeviceData *dd = device_data();
   if (!dd) return NGSX_ERR_CUDA;

@@ -289,8 +289,22 @@ class Expr:
     def __rsub__(self, o):
         return (-self) + o
 
-    _VEC = {"gu", "gv", "n"}
+    # vector-valued atoms: gradients of the trial / test function on the dofs of Vh (gu, gv), the sign-masked gradients on the
+    # x-dofs (gxun = neg_grad(u_x), gxup = pos_grad(u_x), gxvn, gxvp; xfem/xfemdiffops.cpp:44-60) and the level-set normal n
+    _VEC = {"gu", "gv", "n", "gxun", "gxup", "gxvn", "gxvp"}
     _CONTRACT = {frozenset(("gu", "gv")): "gugv", frozenset(("gu", "n")): "gun", frozenset(("gv", "n")): "gvn"}
+
+    @staticmethod
+    def _contract(vec):
+        key = frozenset(vec)
+        if key in Expr._CONTRACT:
+            return Expr._CONTRACT[key]
+        a, b = sorted(vec)
+        trial, test = {"gu", "gxun", "gxup"}, {"gv", "gxvn", "gxvp"}
+        ok = (a in trial and b in test) or (a in test and b in trial) or ((a == "n") != (b == "n"))
+        if not ok or len(key) != 2:
+            raise _lib.NgsxError(-2, f"unsupported product {vec}")
+        return a + "." + b
 
     def __mul__(self, o):
         if isinstance(o, Poly) and not set(o.terms) <= {(0, 0, 0)}:
@@ -306,10 +320,7 @@ class Expr:
                 atoms = list(a1 + a2)
                 vec = [a for a in atoms if a in Expr._VEC]
                 if len(vec) == 2:                      # NGSolve: vector * vector = inner product
-                    key = frozenset(vec)
-                    if key not in Expr._CONTRACT:
-                        raise _lib.NgsxError(-2, f"unsupported product {vec}")
-                    atoms = [a for a in atoms if a not in Expr._VEC] + [Expr._CONTRACT[key]]
+                    atoms = [a for a in atoms if a not in Expr._VEC] + [Expr._contract(vec)]
                 elif len(vec) > 2:
                     raise _lib.NgsxError(-2, "unsupported vector product")
                 out.append((c1 * c2, p1 + p2, tuple(sorted(atoms))))

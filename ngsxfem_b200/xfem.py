@@ -230,6 +230,11 @@ class SymbolicCutBFI:
         if time_order >= 0 or subdivlvl != 0 or deformation is not None or definedon is not None:
             raise NgsxError(-2, "time_order / subdivlvl / deformation / definedon are outside the CUDA path")
         self.lset, self.dt, self.force_intorder, self.definedonelements = lset, int(domain_type), force_intorder, definedonelements
+        self.xterms = None
+        from . import xfes
+        if xfes.has_x_atoms(form):
+            self._init_x(form, xfes)
+            return
         terms = form.collect()
         f = _lib.FormH1()
         difforder_trial, difforder_test = 99, 99
@@ -254,6 +259,28 @@ class SymbolicCutBFI:
             difforder_trial, difforder_test = 0, 0           # proxies u (0) and grad u (1) both present: min = 0
         self.form = f
         self.difforders = (difforder_trial, difforder_test)
+
+    def _init_x(self, form, xfes):
+        """form on the compound space [Vh, XFESpace]: product terms for ngsx_xfem_elmat_h1 (IF elements) + the part living on the
+        dofs of Vh alone, which is all that is left on uncut elements (an XFESpace has no dofs there, xfem/xFESpace.cpp:15-28)"""
+        self.xterms, self.difforders = xfes.xterms_of(form)
+        f = _lib.FormH1()
+        self.has_std = False
+        for c, p, kap, pair, bu, bv in self.xterms:
+            if bu or bv:
+                continue
+            if self.dt == IF:
+                continue                                  # no uncut elements in an interface integral
+            if kap:
+                raise NgsxError(-2, "a cut-ratio weight on a volume term of Vh is outside the CUDA path")
+            if pair == 4 and f.c_stiff == 0.0:
+                f.c_stiff, f.hpow_stiff = c, p
+            elif pair == 0 and f.c_mass == 0.0:
+                f.c_mass, f.hpow_mass = c, p
+            else:
+                raise NgsxError(-2, "volume terms on Vh: one grad(u)*grad(v) and one u*v term are supported")
+            self.has_std = True
+        self.form = f
 
     def intorder(self, fe_order: int) -> int:
         """xfem/symboliccutbfi.cpp:97-113"""
@@ -379,6 +406,7 @@ class BilinearForm:
         self._err = torch.zeros((1, 2), dtype=torch.int64, device=space.mesh.device)     # one {count, first} per integrator
         self._err_armed = False
         self.row_range = None      # (lo, hi): this rank owns CSR rows [lo, hi) (multi-GPU owner-computes partition)
+        self._h1 = getattr(space, "std", space)        # the H1 component (compound space [Vh, XFESpace]: its first component)
 
     def __iadd__(self, integ):
         if not isinstance(integ, (SymbolicCutBFI, SymbolicFacetPatchBFI)):
@@ -404,14 +432,19 @@ class BilinearForm:
         check(L.ngsx_csr_graph_create(fes.ndof, ctypes.byref(g)))
         try:
             els = self._graph_elements()
-            tab = fes.el2dof if els is None else fes.el2dof[els].contiguous()
-            check(L.ngsx_csr_graph_add_table(g, tab.shape[0], fes.nd, _ptr(tab), _stream()))
+            h1 = self._h1
+            tab = h1.el2dof if els is None else h1.el2dof[els].contiguous()
+            check(L.ngsx_csr_graph_add_table(g, tab.shape[0], h1.nd, _ptr(tab), _stream()))
+            if h1 is not fes:                                      # compound space: couplings of the x-dofs on the IF elements
+                ctab = fes.compound_table()
+                if ctab.shape[0]:
+                    check(L.ngsx_csr_graph_add_table(g, ctab.shape[0], ctab.shape[1], _ptr(ctab), _stream()))
             fac = self._graph_facets()
             if fac is not None and fac.numel() > 0:
                 _, f2e = fes.mesh.facets()
                 pe = f2e[fac].long()
-                ptab = torch.cat([fes.el2dof[pe[:, 0]], fes.el2dof[pe[:, 1]]], dim=1).contiguous()
-                check(L.ngsx_csr_graph_add_table(g, ptab.shape[0], 2 * fes.nd, _ptr(ptab), _stream()))
+                ptab = torch.cat([h1.el2dof[pe[:, 0]], h1.el2dof[pe[:, 1]]], dim=1).contiguous()
+                check(L.ngsx_csr_graph_add_table(g, ptab.shape[0], 2 * h1.nd, _ptr(ptab), _stream()))
             nnz = ctypes.c_int64(0)
             check(L.ngsx_csr_graph_finalize(g, ctypes.byref(nnz), _stream()))
             if nnz.value >= 2 ** 31:
@@ -443,15 +476,38 @@ class BilinearForm:
             els = torch.nonzero(de).reshape(-1) if els is None else els[de[els]]
         if els is None:
             els = torch.arange(self.space.mesh.ne, device=self.space.mesh.device)
+        if integ.xterms is not None:                               # the IF elements go through the compound kernel
+            cut = self.space.x.cutinfo.GetElementsOfType(IF).to_bool()
+            els = els[~cut[els]]
         return els
 
-    def _row_plan(self, integ: SymbolicCutBFI) -> _RowPlan:
+    def _x_plan(self, integ: SymbolicCutBFI):
+        """compound integrator: row plan of the Vh part on the uncut elements + row plan over [dofs of Vh | x-dofs] of the IF elements"""
         fes, L = self.space, _lib_()
+        if self._h1 is fes:
+            raise NgsxError(-1, "neg / pos operators need a BilinearForm on FESpace([Vh, XFESpace(Vh)])")
+        plan_a = self._row_plan(integ) if (integ.dt != IF and integ.has_std) else None
+        ctab = fes.compound_table()
+        h = ctypes.c_void_p()
+        lo, hi = self.row_range if self.row_range is not None else (0, fes.ndof)
+        check(L.ngsx_rowplan_create(ctab.shape[0], ctab.shape[1], _ptr(ctab), fes.ndof, _ptr(self.mat.rowptr), _ptr(self.mat.colidx),
+                                    lo, hi, ctypes.byref(h), _stream()))
+        info = (ctypes.c_int64 * 6)()
+        check(L.ngsx_rowplan_info(h, info))
+        plan_b = _RowPlan(fes.x.if_els, ctab, h, tuple(info))
+        plan_b.mats = torch.empty((ctab.shape[0], ctab.shape[1] ** 2), dtype=torch.float64, device=fes.mesh.device)
+        from . import xfes
+        plan_b.xterms = xfes.make_xterms(integ.xterms)
+        plan_b.plan_a = plan_a
+        return plan_b
+
+    def _row_plan(self, integ: SymbolicCutBFI) -> _RowPlan:
+        fes, L = self._h1, _lib_()
         els = self._listed_elements(integ).to(torch.int32).contiguous()
         table = fes.el2dof[els.long()].contiguous()
         h = ctypes.c_void_p()
-        lo, hi = self.row_range if self.row_range is not None else (0, fes.ndof)
-        check(L.ngsx_rowplan_create(els.numel(), fes.nd, _ptr(table), fes.ndof, _ptr(self.mat.rowptr), _ptr(self.mat.colidx),
+        lo, hi = self.row_range if self.row_range is not None else (0, self.space.ndof)
+        check(L.ngsx_rowplan_create(els.numel(), fes.nd, _ptr(table), self.space.ndof, _ptr(self.mat.rowptr), _ptr(self.mat.colidx),
                                     lo, hi, ctypes.byref(h), _stream()))
         info = (ctypes.c_int64 * 6)()
         check(L.ngsx_rowplan_info(h, info))
@@ -461,7 +517,9 @@ class BilinearForm:
         if k in self._plans:
             return self._plans[k]
         fes, L = self.space, _lib_()
-        if isinstance(integ, SymbolicCutBFI) and self.assembly == "rows":
+        if isinstance(integ, SymbolicCutBFI) and integ.xterms is not None:
+            plan = self._x_plan(integ)
+        elif isinstance(integ, SymbolicCutBFI) and self.assembly == "rows":
             try:
                 plan = self._row_plan(integ)
             except NgsxError as exc:
@@ -524,7 +582,8 @@ class BilinearForm:
         plans = [self._plan_for(k, integ) for k, integ in enumerate(self.integrators)]
         # a single row plan that covers every stored entry overwrites its rows: no SetZero pass, each value written once
         # (with a row range: the rank's rows are one contiguous CSR span, the other rows belong to other ranks and stay untouched)
-        overwrite = len(plans) == 1 and isinstance(self.integrators[0], SymbolicCutBFI) and isinstance(plans[0], _RowPlan) and \
+        overwrite = len(plans) == 1 and isinstance(self.integrators[0], SymbolicCutBFI) and self.integrators[0].xterms is None and \
+            isinstance(plans[0], _RowPlan) and \
             plans[0].nnz_covered == (self.mat.nnz if self.row_range is None else plans[0].nnz_hi - plans[0].nnz_lo)
         if not overwrite:
             self.mat.vals.zero_()
@@ -535,6 +594,8 @@ class BilinearForm:
             plan = plans[k]
             if isinstance(integ, SymbolicFacetPatchBFI):
                 self._assemble_facetpatch(integ, plan)
+            elif integ.xterms is not None:
+                self._assemble_x(integ, plan, k)
             elif isinstance(plan, _RowPlan):
                 lv = _lset_vec(integ.lset)
                 check(L.ngsx_assemble_csr_rows_h1(mesh_c, _ptr(lv), fes.order, integ.dt, integ.intorder(fes.order), ctypes.byref(integ.form),
@@ -558,6 +619,25 @@ class BilinearForm:
         if n:
             raise NgsxError(-4, f"{n} element(s) carry a level set the reference rejects (first: element {first}): "
                                 "'You tried to cut a simplex with a plain geometry lset function'")
+
+    def _assemble_x(self, integ, plan, k):
+        """compound integrator: Vh part on the uncut elements through the H1 row gather, then the (2 nd)^2 blocks of the IF elements
+        (ngsx_xfem_elmat_h1) through the matrix-fed gather; both add in plan order"""
+        L = _lib_()
+        fes, h1 = self.space, self._h1
+        lv = _lset_vec(integ.lset)
+        io = integ.intorder(h1.order)
+        mesh_c = ctypes.byref(fes.mesh.c_struct())
+        if plan.plan_a is not None:
+            pa = plan.plan_a
+            check(L.ngsx_assemble_csr_rows_h1(mesh_c, _ptr(lv), h1.order, integ.dt, io, ctypes.byref(integ.form), pa.els.numel(), _ptr(pa.els),
+                                              pa.handle, 1, _ptr(self.mat.vals), _ptr(self._err[k]), _stream()))
+            self._err_armed = True
+        n = plan.els.numel()
+        if n:
+            check(L.ngsx_xfem_elmat_h1(mesh_c, _ptr(lv), h1.order, integ.dt, io, len(integ.xterms), plan.xterms, n, _ptr(plan.els),
+                                       _ptr(fes.x.xsign), _ptr(fes.x.cutinfo.ratio), _ptr(plan.mats), _stream()))
+            check(L.ngsx_assemble_csr_rows_mats(plan.handle, _ptr(plan.mats), 1, _ptr(self.mat.vals), _stream()))
 
     def _assemble_facetpatch(self, integ, plan):
         """numeric phase: merged patch blocks (ngsx_facetpatch_cmat_h1), then the owner-computes gather adds them to the rows
@@ -636,3 +716,7 @@ class LinearForm:
                                          integ.intorder(fes.order), ctypes.byref(poly), plan.els.numel(), _ptr(plan.els), _ptr(plan.table),
                                          plan.ncolors, plan.h_color_ptr, plan.group, _ptr(self.vec), _stream()))
         return self
+
+
+# XFESpace and the sign-masked operators (xfem/python_xfem.cpp:321-448, python/__init__.py:22-105, 397-409)
+from .xfes import XFESpace, CutRatioGF, neg, pos, neg_grad, pos_grad, extend, extend_grad  # noqa: E402,F401

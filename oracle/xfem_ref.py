@@ -1,0 +1,77 @@
+"""TEST INFRASTRUCTURE -- CPU restatement of the reference's XFEM element matrices (numpy, small cases only).
+
+Follows the reference directly, not the CUDA decomposition:
+  * XFESpace::Update (xfem/xFESpace.cpp:244-366): x-dofs = base dofs of IF elements in base-dof order, domofdof = NEG unless
+    the node of the dof touches an uncut element, then INVERT(domain of that element) (dom_of_node: xfem/cutinfo.cpp:152-186);
+  * DiffOpX<D, RNEG/RPOS/RNEG_GRAD/RPOS_GRAD>::GenerateMatrix (xfem/xfemdiffops.cpp:8-66): B-row i = base shape (gradient) if
+    xsign[i] == domain of the operator, else 0;
+  * the two-phase Nitsche forms of py_tutorials/nxfem.py:77-107 evaluated point by point on the cut rules
+    (xfem/symboliccutbfi.cpp:73-315; intorder = 2 order - difforders, :97-107).
+The cut rules and H1 shapes come from the pinned C oracle (oracle/ngsx_oracle.c, checked against the compiled reference and
+the reference's known-answer tests).  Parity of the mask algebra itself is pinned only by this restatement: "parity unpinned"
+for the XFEM row in the sense of the task statement (no golden vector of the reference exists for it; the reference's
+Python bindings do not build here)."""
+import numpy as np
+
+from . import orc
+
+NEG, POS, IF = 0, 1, 2
+
+
+def xfespace(dim, order, el2v, el2dof, ndof_base, nv, dom):
+    """returns (basedof2xdof [ndof_base], domofdof [nx]) -- xfem/xFESpace.cpp:276-366 for an H1 space with vertex + edge dofs"""
+    active = np.zeros(ndof_base, dtype=bool)
+    for e in np.nonzero(dom == IF)[0]:
+        active[el2dof[e]] = True
+    b2x = np.where(active, np.cumsum(active) - 1, -1)
+    # dom_of_node per base dof (vertex dofs: vertex nodes; edge dofs: edge nodes): IF unless adjacent to an uncut element
+    node_dom = np.full(ndof_base, IF, dtype=np.int64)
+    for e in np.nonzero(dom != IF)[0]:
+        node_dom[el2dof[e]] = dom[e]
+    domofdof = np.full(int(active.sum()), NEG, dtype=np.int64)
+    for b in np.nonzero(active)[0]:
+        if node_dom[b] != IF:
+            domofdof[b2x[b]] = 1 - node_dom[b]
+    return b2x, domofdof
+
+
+def _bvectors(dim, order, vnums, pmat, xi, xsign, nrm):
+    """B-vectors of the proxies at one point over [dofs of Vh | x-dofs]: values U[k], gradients G[k] (k = NEG, POS)"""
+    s, ds = orc.h1_shape(dim, order, vnums, xi[:dim])
+    J = (pmat[:dim] - pmat[dim]).T
+    g = ds @ np.linalg.inv(J)
+    nd = len(s)
+    U, G = [], []
+    for k in (NEG, POS):
+        m = (np.asarray(xsign) == k).astype(float)
+        U.append(np.concatenate([s, m * s]))
+        G.append(np.vstack([g, m[:, None] * g]))
+    return U, G
+
+
+def nxfem_elmat(dim, order, vnums, pmat, ls, xsign, kappa_neg, alpha, stab_factor):
+    """compound element matrix (2 nd x 2 nd) of the three integrators of py_tutorials/nxfem.py:98-107 on one element:
+    NEG: alpha0 gradu0.gradv0, POS: alpha1 gradu1.gradv1, IF: avgflux_u [v] + avgflux_v [u] + stab [u][v],
+    stab = stab_factor (alpha0 + alpha1) / h.  xsign = None: uncut element (no x-dofs, block nd x nd)."""
+    J = (pmat[:dim] - pmat[dim]).T
+    meas = abs(np.linalg.det(J))
+    h = meas ** (1.0 / dim)
+    gphi = np.linalg.inv(J).T @ (ls[:dim] - ls[dim])
+    nrm = gphi / np.linalg.norm(gphi)
+    nd = orc.load().orc_h1_ndof(dim, order)
+    xs = [-1] * nd if xsign is None else xsign
+    A = np.zeros((2 * nd, 2 * nd))
+    kappa = (kappa_neg, 1.0 - kappa_neg)
+    for dt in (NEG, POS):
+        npt, pts, w = orc.cut_rule(dim, pmat, ls, dt, 2 * order - 2)
+        for q in range(max(npt, 0)):
+            U, G = _bvectors(dim, order, vnums, pmat, pts[q], xs, nrm)
+            A += meas * w[q] * alpha[dt] * (G[dt] @ G[dt].T)
+    npt, pts, w = orc.cut_rule(dim, pmat, ls, IF, 2 * order)
+    stab = stab_factor * (alpha[0] + alpha[1]) / h
+    for q in range(max(npt, 0)):
+        U, G = _bvectors(dim, order, vnums, pmat, pts[q], xs, nrm)
+        flux = -sum(kappa[k] * alpha[k] * (G[k] @ nrm) for k in (NEG, POS))
+        jump = U[NEG] - U[POS]
+        A += meas * w[q] * (np.outer(jump, flux) + np.outer(flux, jump) + stab * np.outer(jump, jump))
+    return A if xsign is not None else A[:nd, :nd]

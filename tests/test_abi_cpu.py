@@ -117,3 +117,35 @@ def test_host_mirror_parses_tutorial_forms():
         with pytest.raises(_lib.NgsxError):
             bad()
     assert (xfem.NEG, xfem.POS, xfem.IF) == (0, 1, 2) and int(xfem.HASNEG) == 5 and int(xfem.ANY) == 7   # utils/ngsxstd.hpp
+
+
+def test_xfem_form_expansion():
+    """f-2 host logic: the Nitsche-XFEM forms of py_tutorials/nxfem.py:77-107 expand into the product terms of ngsx_xterm with
+    the reference's differential orders (xfem/symboliccutbfi.cpp:97-101, xfem/xfemdiffops.hpp:24)"""
+    from ngsxfem_b200 import _lib, ngs, xfes
+    from ngsxfem_b200.ngs import Expr
+    u_std, v_std = Expr.atom("u"), Expr.atom("v")
+    u_x, v_x = xfes.XProxy("u"), xfes.XProxy("v")
+    alpha = [1.0, 2.0]
+    n, h = ngs.LevelsetNormal(), ngs.specialcf.mesh_size
+    k0 = xfes.CutRatioGF(None)
+    kappa = (k0, 1.0 - k0)
+    u = [u_std + op(u_x) for op in (xfes.neg, xfes.pos)]
+    v = [v_std + op(v_x) for op in (xfes.neg, xfes.pos)]
+    gu = [ngs.grad(u_std) + op(u_x) for op in (xfes.neg_grad, xfes.pos_grad)]
+    gv = [ngs.grad(v_std) + op(v_x) for op in (xfes.neg_grad, xfes.pos_grad)]
+    terms, do = xfes.xterms_of(alpha[1] * gu[1] * gv[1])
+    assert do == (1, 1) and sorted(terms) == sorted([(2.0, 0, 0, 4, bu, bv) for bu in (0, 2) for bv in (0, 2)])
+    fu = sum([-kappa[i] * alpha[i] * gu[i] * n for i in (0, 1)])
+    fv = sum([-kappa[i] * alpha[i] * gv[i] * n for i in (0, 1)])
+    stab = 20 * (alpha[0] + alpha[1]) / h
+    terms, do = xfes.xterms_of(fu * (v[0] - v[1]) + fv * (u[0] - u[1]) + stab * (u[0] - u[1]) * (v[0] - v[1]))
+    assert do == (0, 0) and len(terms) == 24
+    # the jump [v] = neg(v_x) - pos(v_x): no term may test with the dofs of Vh, and the penalty carries h^-1
+    assert all(bv != 0 for c, p, k, pair, bu, bv in terms if pair in (0, 1))
+    assert sorted((c, p) for c, p, k, pair, bu, bv in terms if pair == 0) == [(-60.0, -1), (-60.0, -1), (60.0, -1), (60.0, -1)]
+    assert xfes.has_x_atoms(fu * v[0]) and not xfes.has_x_atoms(ngs.grad(u_std) * ngs.grad(v_std))
+    with pytest.raises(_lib.NgsxError):
+        xfes.xterms_of(k0 * k0 * u[0] * v[0])
+    with pytest.raises(_lib.NgsxError):
+        xfes.neg(u_std)

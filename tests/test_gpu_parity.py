@@ -373,6 +373,80 @@ def test_ghost_penalty_row_gather(X, dim, fo):
     assert diff <= 1e-11 * abs(ref).max()
 
 
+@pytest.mark.parametrize("dim,fo", [(2, 1), (2, 2), (3, 1), (3, 2)])
+def test_xfem_nitsche_compound(X, dim, fo):
+    """f-2: two-phase Nitsche-XFEM operator of py_tutorials/nxfem.py:62-107 on FESpace([Vh, XFESpace(Vh)]) with the sign-masked
+    operators neg / pos / neg_grad / pos_grad and CutRatioGF averages, vs the numpy restatement of the reference (oracle/xfem_ref.py)."""
+    from oracle import orc, xfem_ref
+    import scipy.sparse as sp
+    xf, ngs = X.xfem, X.ngs
+    if dim == 2:
+        mesh = ngs.Mesh(X.meshes.MakeStructured2DMesh(6, lo=(-1.5, -1.5), hi=(1.5, 1.5)))
+        lset = ngs.SphereLevelset((0.05, -0.02), 1.0)
+    else:
+        mesh = ngs.Mesh(X.meshes.MakeStructured3DMesh(6))
+        lset = ngs.SphereLevelset((0.52, 0.49, 0.51), 0.41)
+    gf = ngs.GridFunction(ngs.H1(mesh, order=1))
+    xf.InterpolateToP1(lset, gf)
+    ci = xf.CutInfo(mesh, gf)
+    Vh = ngs.H1(mesh, order=fo)
+    Vhx = xf.XFESpace(Vh, ci)
+    from ngsxfem_b200.xfes import FESpace
+    VhG = FESpace([Vh, Vhx])
+    alpha = [1.0, 2.0]
+    n = ngs.LevelsetNormal(gf)
+    h = ngs.specialcf.mesh_size
+    kappa = (xf.CutRatioGF(ci), 1.0 - xf.CutRatioGF(ci))
+    stab = 20 * (alpha[1] + alpha[0]) / h
+    (u_std, u_x), (v_std, v_x) = VhG.TrialFunction(), VhG.TestFunction()
+    u = [u_std + op(u_x) for op in (xf.neg, xf.pos)]
+    v = [v_std + op(v_x) for op in (xf.neg, xf.pos)]
+    gradu = [ngs.grad(u_std) + op(u_x) for op in (xf.neg_grad, xf.pos_grad)]
+    gradv = [ngs.grad(v_std) + op(v_x) for op in (xf.neg_grad, xf.pos_grad)]
+    average_flux_u = sum([-kappa[i] * alpha[i] * gradu[i] * n for i in (0, 1)])
+    average_flux_v = sum([-kappa[i] * alpha[i] * gradv[i] * n for i in (0, 1)])
+    a = xf.BilinearForm(VhG)
+    a += xf.SymbolicBFI(levelset_domain={"levelset": gf, "domain_type": NEG}, form=alpha[0] * gradu[0] * gradv[0])
+    a += xf.SymbolicBFI(levelset_domain={"levelset": gf, "domain_type": POS}, form=alpha[1] * gradu[1] * gradv[1])
+    a += xf.SymbolicBFI(levelset_domain={"levelset": gf, "domain_type": IF},
+                        form=average_flux_u * (v[0] - v[1]) + average_flux_v * (u[0] - u[1]) + stab * (u[0] - u[1]) * (v[0] - v[1]))
+    assert a.integrators[0].intorder(fo) == 2 * fo - 2 and a.integrators[2].intorder(fo) == 2 * fo
+    a.Assemble()
+    first = a.mat.vals.clone()
+    a.mat.vals.fill_(float("nan"))
+    a.Assemble()
+    assert torch.equal(first, a.mat.vals)                                   # bitwise reproducible
+    a.check_degenerate()
+    # --- oracle ---
+    el2v, vert, ls, e2d = mesh.el2v.cpu().numpy(), mesh.vert.cpu().numpy(), gf.vec.cpu().numpy(), Vh.el2dof.cpu().numpy()
+    dom, ratio, nerr = orc.cutinfo_mesh(dim, el2v, vert, ls)
+    assert nerr == 0
+    b2x, dod = xfem_ref.xfespace(dim, fo, el2v, e2d, Vh.ndof, mesh.nv, dom)
+    assert Vhx.ndof == len(dod) and VhG.ndof == Vh.ndof + len(dod)
+    assert np.array_equal(Vhx.basedof2xdof.cpu().numpy(), b2x) and np.array_equal(Vhx.domofdof.cpu().numpy(), dod)
+    assert set(np.unique(dod)) <= {0, 1} and len(np.unique(dod)) == 2
+    e_if = int(np.nonzero(dom == 2)[0][0])
+    assert Vhx.GetDofNrs(e_if) == list(b2x[e2d[e_if]]) and Vhx.GetDomainNrs(e_if) == list(dod[b2x[e2d[e_if]]])
+    assert Vhx.GetDofNrs(int(np.nonzero(dom != 2)[0][0])) == [] and Vhx.BaseDofOfXDof(0) == int(np.nonzero(b2x == 0)[0][0])
+    A = sp.lil_matrix((VhG.ndof, VhG.ndof))
+    for e in range(mesh.ne):
+        pm, l = vert[el2v[e]], ls[el2v[e]]
+        if dom[e] == 2:
+            xs = dod[b2x[e2d[e]]]
+            em = xfem_ref.nxfem_elmat(dim, fo, el2v[e], pm, l, xs, ratio[e], alpha, 20.0)
+            d = np.concatenate([e2d[e], Vh.ndof + b2x[e2d[e]]])
+        else:
+            em = xfem_ref.nxfem_elmat(dim, fo, el2v[e], pm, l, None, ratio[e], alpha, 20.0)
+            d = e2d[e]
+        for i in range(len(d)):
+            for j in range(len(d)):
+                A[d[i], d[j]] += em[i, j]
+    ref = A.tocsr()
+    got = a.mat.to_scipy()
+    assert abs(got - ref).max() <= 1e-11 * abs(ref).max()
+    assert abs(got - got.T).max() <= 1e-11 * abs(ref).max()                  # the Nitsche form is symmetric
+
+
 def test_unsupported_paths_raise(X):
     mesh = X.ngs.Mesh(X.meshes.MakeStructured2DMesh(2))
     gf = X.ngs.GridFunction(X.ngs.H1(mesh, order=1))
