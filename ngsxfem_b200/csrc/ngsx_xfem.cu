@@ -24,6 +24,7 @@ struct XTermsDev {
   int n;
   double coef[XMAXTERMS];
   int8_t hpow[XMAXTERMS], kappa[XMAXTERMS], pair[XMAXTERMS], blk_u[XMAXTERMS], blk_v[XMAXTERMS];
+  int8_t cls[10];             // terms are sorted by class blk_v * 3 + blk_u; class c = terms [cls[c], cls[c + 1])
 };
 
 template <int DIM>
@@ -173,8 +174,8 @@ __global__ void __launch_bounds__(XW * 32) k_xfem(ngsx_mesh M, const double *__r
       // blk 0: std dofs; blk 1 / 2: x dofs whose sign is NEG / POS
       const int cI = bI ? 1 + (int)sg[i] : 0, cJ = bJ ? 1 + (int)sg[j] : 0;
       double v = 0.0;
-      for (int t = 0; t < X.n; t++) {
-        if (X.blk_v[t] != cI || X.blk_u[t] != cJ) continue;
+      const int c = cI * 3 + cJ;
+      for (int t = X.cls[c]; t < X.cls[c + 1]; t++) {
         const int pr = X.pair[t];
         const double b = pr == 0 ? base[i * ND + j] : (pr == 1 ? base[NE + i * ND + j] : (pr == 2 ? base[NE + j * ND + i]
                          : (pr == 3 ? base[2 * NE + i * ND + j] : base[3 * NE + i * ND + j])));
@@ -225,8 +226,22 @@ extern "C" int ngsx_xfem_elmat_h1(const ngsx_mesh *mesh, const double *lset_v, i
     const ngsx_xterm &s = h_terms[t];
     NGSX_REQUIRE(s.pair >= 0 && s.pair <= 4 && s.kappa >= 0 && s.kappa <= 2 && s.blk_u >= 0 && s.blk_u <= 2 && s.blk_v >= 0 && s.blk_v <= 2 &&
                  s.hpow >= -8 && s.hpow <= 8, "xfem_elmat: bad term");
-    X.coef[t] = s.coef; X.hpow[t] = (int8_t)s.hpow; X.kappa[t] = (int8_t)s.kappa; X.pair[t] = (int8_t)s.pair;
-    X.blk_u[t] = (int8_t)s.blk_u; X.blk_v[t] = (int8_t)s.blk_v;
+  }
+  {
+    // stable counting sort by (test block, trial block): an entry of the compound block only walks its own class; the order of
+    // the terms inside a class -- the summation order -- is the caller's
+    int o = 0;
+    for (int c = 0; c < 9; c++) {
+      X.cls[c] = (int8_t)o;
+      for (int t = 0; t < nterms; t++) {
+        const ngsx_xterm &s = h_terms[t];
+        if (s.blk_v * 3 + s.blk_u != c) continue;
+        X.coef[o] = s.coef; X.hpow[o] = (int8_t)s.hpow; X.kappa[o] = (int8_t)s.kappa; X.pair[o] = (int8_t)s.pair;
+        X.blk_u[o] = (int8_t)s.blk_u; X.blk_v[o] = (int8_t)s.blk_v;
+        o++;
+      }
+    }
+    X.cls[9] = (int8_t)o;
   }
   if (nlist == 0) return NGSX_OK;
   cudaStream_t st = as_stream(stream);
