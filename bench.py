@@ -105,15 +105,16 @@ def build_problem(nx, device, rank=0, world=1, group=6):
     hasneg = ci.GetElementsOfType(xfem.HASNEG)
     active = hasneg.nonzero()
     n_total = active.numel()
-    row_range = None
+    row_owner = None
     if world > 1:
-        # owner-computes partition (ngsxfem_b200/partition.py): rank r owns a contiguous block of CSR rows with 1/world of the
-        # (row, element) pairs and lists every HASNEG element touching them (halo elements are evaluated twice, nothing is exchanged)
+        # owner-computes partition (ngsxfem_b200/partition.py): contiguous chunks of the HASNEG element list per rank, a CSR row
+        # belongs to the rank of the first listed element touching it; the rank lists every HASNEG element touching one of its
+        # rows (halo elements are evaluated twice, nothing is exchanged)
         from ngsxfem_b200 import partition
         from ngsxfem_b200.ngs import BitArray
-        blocks = partition.row_blocks(Vh.el2dof[active], Vh.ndof, world)
-        row_range = blocks[rank]
-        mine_els = partition.elements_touching(Vh.el2dof, active, *row_range)
+        owner = partition.row_owners(Vh.el2dof[active], Vh.ndof, world)
+        row_owner = (owner, rank)
+        mine_els = partition.elements_of_owner(Vh.el2dof, active, owner, rank)
         mine = torch.zeros(mesh.ne, dtype=torch.bool, device=device)
         mine[mine_els] = True
         restr = BitArray.from_bool(mine)
@@ -122,7 +123,7 @@ def build_problem(nx, device, rank=0, world=1, group=6):
     u, v = Vh.TnT()
     a = xfem.RestrictedBilinearForm(Vh, element_restriction=restr)
     a.group_size = group
-    a.row_range = row_range
+    a.row_owner = row_owner
     a += xfem.SymbolicBFI(levelset_domain={"levelset": lsetp1, "domain_type": xfem.NEG}, form=grad(u) * grad(v) + u * v,
                           definedonelements=restr)
     mesh_int = mesh                                      # this rank's elements of CutInfo.Update and the Integrate() reductions
@@ -212,8 +213,13 @@ def run_b200(args):
 
     # ---- e2e: level set from pinned host memory every step, CSR values + integrals back to the host ----------------
     h_lset = lsetp1.vec.cpu().pin_memory()
-    v_lo, v_hi = (plan.nnz_lo, plan.nnz_hi) if (world > 1 and hasattr(plan, "nnz_lo")) else (0, a.mat.nnz)   # the CSR span this rank owns
-    h_vals = torch.empty(v_hi - v_lo, dtype=torch.float64).pin_memory()
+    own_idx = None                                       # CSR entries of the rows this rank owns (N > 1: compacted before the download)
+    if world > 1:
+        rows_of = torch.repeat_interleave(torch.arange(P["Vh"].ndof, device=dev), a.mat.rowptr[1:] - a.mat.rowptr[:-1])
+        own_idx = torch.nonzero(a.row_owner[0][rows_of] == rank).reshape(-1)
+        del rows_of
+    n_own = a.mat.nnz if own_idx is None else own_idx.numel()
+    h_vals = torch.empty(n_own, dtype=torch.float64).pin_memory()
     h_sc = torch.empty(2, dtype=torch.float64).pin_memory()
     from ngsxfem_b200.ngs import GridFunction
     gf_in = GridFunction(lsetp1.space)
@@ -222,7 +228,8 @@ def run_b200(args):
         gf_in.vec.copy_(h_lset, non_blocking=True)                       # H2D: this step's input
         xfem.InterpolateToP1(gf_in, lsetp1)                              # GridFunction branch + clamp
         s_if, s_neg = step(None)
-        h_vals.copy_(a.mat.vals[v_lo:v_hi], non_blocking=True)           # D2H: the assembled operator (this rank's rows)
+        src = a.mat.vals if own_idx is None else a.mat.vals[own_idx]     # this rank's rows
+        h_vals.copy_(src, non_blocking=True)                             # D2H: the assembled operator
         h_sc.copy_(torch.cat([s_if, s_neg]), non_blocking=True)
         torch.cuda.current_stream().synchronize()
         a.check_degenerate()                                             # the reference throws from inside Assemble; here: after the sync
@@ -285,7 +292,7 @@ def run_b200(args):
                    "ne": mesh.ne, "hasneg_elements": n_global, "nnz": nnz_global, "assembly": a.assembly, "group": args.group, "colors": plan.ncolors,
                    "setup_s_untimed": round(setup_s, 2), "stage_ms": {"classify": cl_ms, "assemble": as_ms, "integrate": in_ms},
                    "l2": "inputs larger than L2 (CSR values + pair descriptors + mesh > 1.4 GB touched per step vs 126 MB L2); no explicit flush",
-                   "partition": "owner-computes: contiguous CSR row blocks per rank balanced by (row, element) pairs, halo elements re-evaluated, no interface-row exchange; element blocks for Integrate, scalars all-reduced (NCCL)"},
+                   "partition": "owner-computes: contiguous chunks of the HASNEG element list per rank, a CSR row belongs to the rank of the first listed element touching it, halo elements re-evaluated, no interface-row exchange; element blocks for Integrate, scalars all-reduced (NCCL)"},
         "roofline": {"bound": "hbm", "kernel": "k_rows<10,6> (owner-computes row gather: every CSR value of the assembled operator written once)",
                      "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": traffic,
                      "peak_source": peak_src, "algorithmic_bytes_per_element": ALGO_BYTES_SCATTER,

@@ -177,6 +177,13 @@ int ngsx_assemble_vec_h1(const ngsx_mesh *mesh, const double *lset_v, int fe_ord
 typedef struct ngsx_rowplan ngsx_rowplan;   /* opaque, owns device buffers (pair descriptors, geometry factors, cut-element matrices) */
 int ngsx_rowplan_create(int64_t nlist, int32_t nd, const int32_t *table, int64_t ndof, const int64_t *rowptr, const int32_t *colidx,
                         int64_t row_lo, int64_t row_hi, ngsx_rowplan **out, void *stream);
+/* Ownership by an arbitrary row set instead of a range: the plan covers the rows r with row_owner[r] == me (row_owner: device
+ * int32 [ndof]).  Used by the multi-GPU partition: contiguous blocks of the ELEMENT list per rank, a row belongs to the rank of
+ * the first listed element that touches it (ngsxfem_b200/partition.py) -- contiguous dof ranges would hand every rank all
+ * vertex rows of an H1 space numbered "vertices, then edges".  The window of a tile may span rows of other owners; their
+ * entries in the caller's (rank-local) value array are scratch. */
+int ngsx_rowplan_create_owned(int64_t nlist, int32_t nd, const int32_t *table, int64_t ndof, const int64_t *rowptr, const int32_t *colidx,
+                              const int32_t *row_owner, int32_t me, ngsx_rowplan **out, void *stream);
 /* h_info[0..5] = {non-empty rows, (row, element) pairs, CSR entries covered by the plan's rows, longest row, first covered CSR
  * entry, one past the last covered CSR entry} */
 int ngsx_rowplan_info(const ngsx_rowplan *plan, int64_t *h_info);

@@ -71,6 +71,7 @@ SIGNATURES = {
     "ngsx_assemble_vec_h1": (c_int, [ctypes.POINTER(Mesh), c_void_p, c_int, c_int, c_int, ctypes.POINTER(Poly), c_i64, c_void_p,
                                      c_void_p, c_i32, c_void_p, c_i32, c_void_p, c_void_p]),
     "ngsx_rowplan_create": (c_int, [c_i64, c_i32, c_void_p, c_i64, c_void_p, c_void_p, c_i64, c_i64, ctypes.POINTER(c_void_p), c_void_p]),
+    "ngsx_rowplan_create_owned": (c_int, [c_i64, c_i32, c_void_p, c_i64, c_void_p, c_void_p, c_void_p, c_i32, ctypes.POINTER(c_void_p), c_void_p]),
     "ngsx_rowplan_info": (c_int, [c_void_p, ctypes.POINTER(c_i64)]),
     "ngsx_rowplan_destroy": (c_int, [c_void_p]),
     "ngsx_assemble_csr_rows_h1": (c_int, [ctypes.POINTER(Mesh), c_void_p, c_int, c_int, c_int, ctypes.POINTER(FormH1), c_i64, c_void_p,

@@ -22,12 +22,14 @@ namespace ngsx {
 // key = (row, local row i, list index k): the pairs of a row are walked grouped by i, so that the lanes of a warp mostly
 // read the same rows of the reference tables in the same step (shared-memory broadcast instead of distinct wavefronts)
 __global__ void __launch_bounds__(256) k_pair_keys(int64_t npairs, int nd, int64_t nlist, const int32_t *__restrict__ table, int64_t row_lo,
-                                                  int64_t row_hi, uint64_t *__restrict__ keys) {
+                                                  int64_t row_hi, const int32_t *__restrict__ row_owner, int32_t me, uint64_t *__restrict__ keys) {
   int64_t p = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (p >= npairs) return;
   int32_t r = table[p];
   const int64_t k = p / nd, i = p - k * nd;
-  keys[p] = (r < row_lo || r >= row_hi) ? ~0ULL : (((uint64_t)(uint32_t)r << 32) | (uint64_t)(i * nlist + k));
+  bool mine = r >= row_lo && r < row_hi;
+  if (mine && row_owner) mine = row_owner[r] == me;
+  keys[p] = mine ? (((uint64_t)(uint32_t)r << 32) | (uint64_t)(i * nlist + k)) : ~0ULL;
 }
 
 __global__ void k_lower_bound(int64_t n, const uint64_t *__restrict__ keys, uint64_t target, int64_t *out) {
@@ -432,8 +434,22 @@ int ngsx_rowplan_info(const ngsx_rowplan *P, int64_t *h_info) {
   return NGSX_OK;
 }
 
+static int rowplan_create(int64_t nlist, int32_t nd, const int32_t *table, int64_t ndof, const int64_t *rowptr, const int32_t *colidx,
+                          int64_t row_lo, int64_t row_hi, const int32_t *row_owner, int32_t me, ngsx_rowplan **out, void *stream);
+
 int ngsx_rowplan_create(int64_t nlist, int32_t nd, const int32_t *table, int64_t ndof, const int64_t *rowptr, const int32_t *colidx,
                         int64_t row_lo, int64_t row_hi, ngsx_rowplan **out, void *stream) {
+  return rowplan_create(nlist, nd, table, ndof, rowptr, colidx, row_lo, row_hi, nullptr, 0, out, stream);
+}
+
+int ngsx_rowplan_create_owned(int64_t nlist, int32_t nd, const int32_t *table, int64_t ndof, const int64_t *rowptr, const int32_t *colidx,
+                              const int32_t *row_owner, int32_t me, ngsx_rowplan **out, void *stream) {
+  if (!row_owner) { set_error("rowplan_create_owned: row_owner is NULL"); return NGSX_ERR_ARG; }
+  return rowplan_create(nlist, nd, table, ndof, rowptr, colidx, 0, -1, row_owner, me, out, stream);
+}
+
+static int rowplan_create(int64_t nlist, int32_t nd, const int32_t *table, int64_t ndof, const int64_t *rowptr, const int32_t *colidx,
+                          int64_t row_lo, int64_t row_hi, const int32_t *row_owner, int32_t me, ngsx_rowplan **out, void *stream) {
   NGSX_REQUIRE(out && nlist >= 0 && nd > 0 && nd <= 27 && ndof >= 0 && ndof < (1LL << 31) && rowptr, "rowplan_create: bad arguments");
   NGSX_REQUIRE(nlist == 0 || (table && colidx), "rowplan_create: table / colidx are NULL");
   NGSX_REQUIRE(nlist * nd < (1LL << 32), "rowplan_create: more than 2^32 (element, dof) pairs");
@@ -464,7 +480,7 @@ int ngsx_rowplan_create(int64_t nlist, int32_t nd, const int32_t *table, int64_t
   PLAN_CUDA(cudaMalloc(&d_bad, sizeof(int)));
   PLAN_CUDA(cudaMemsetAsync(d_stat, 0, 4 * sizeof(unsigned long long), st));
   PLAN_CUDA(cudaMemsetAsync(d_bad, 0, sizeof(int), st));
-  k_pair_keys<<<(unsigned)((nall + 255) / 256), 256, 0, st>>>(nall, nd, nlist, table, row_lo, row_hi, keys);
+  k_pair_keys<<<(unsigned)((nall + 255) / 256), 256, 0, st>>>(nall, nd, nlist, table, row_lo, row_hi, row_owner, me, keys);
   cub::DoubleBuffer<uint64_t> db(keys, alt);
   size_t tmp_bytes = 0;
   PLAN_CUDA(cub::DeviceRadixSort::SortKeys(nullptr, tmp_bytes, db, nall, 0, 64, st));

@@ -406,6 +406,7 @@ class BilinearForm:
         self._err = torch.zeros((1, 2), dtype=torch.int64, device=space.mesh.device)     # one {count, first} per integrator
         self._err_armed = False
         self.row_range = None      # (lo, hi): this rank owns CSR rows [lo, hi) (multi-GPU owner-computes partition)
+        self.row_owner = None      # (owner int32 [ndof] on the device, me): this rank owns the rows with owner == me
         self._h1 = getattr(space, "std", space)        # the H1 component (compound space [Vh, XFESpace]: its first component)
 
     def __iadd__(self, integ):
@@ -507,8 +508,12 @@ class BilinearForm:
         table = fes.el2dof[els.long()].contiguous()
         h = ctypes.c_void_p()
         lo, hi = self.row_range if self.row_range is not None else (0, self.space.ndof)
-        check(L.ngsx_rowplan_create(els.numel(), fes.nd, _ptr(table), self.space.ndof, _ptr(self.mat.rowptr), _ptr(self.mat.colidx),
-                                    lo, hi, ctypes.byref(h), _stream()))
+        if self.row_owner is not None:
+            check(L.ngsx_rowplan_create_owned(els.numel(), fes.nd, _ptr(table), self.space.ndof, _ptr(self.mat.rowptr), _ptr(self.mat.colidx),
+                                              _ptr(self.row_owner[0]), int(self.row_owner[1]), ctypes.byref(h), _stream()))
+        else:
+            check(L.ngsx_rowplan_create(els.numel(), fes.nd, _ptr(table), self.space.ndof, _ptr(self.mat.rowptr), _ptr(self.mat.colidx),
+                                        lo, hi, ctypes.byref(h), _stream()))
         info = (ctypes.c_int64 * 6)()
         check(L.ngsx_rowplan_info(h, info))
         return _RowPlan(els, table, h, tuple(info))
@@ -584,7 +589,8 @@ class BilinearForm:
         # (with a row range: the rank's rows are one contiguous CSR span, the other rows belong to other ranks and stay untouched)
         overwrite = len(plans) == 1 and isinstance(self.integrators[0], SymbolicCutBFI) and self.integrators[0].xterms is None and \
             isinstance(plans[0], _RowPlan) and \
-            plans[0].nnz_covered == (self.mat.nnz if self.row_range is None else plans[0].nnz_hi - plans[0].nnz_lo)
+            (self.row_owner is not None or
+             plans[0].nnz_covered == (self.mat.nnz if self.row_range is None else plans[0].nnz_hi - plans[0].nnz_lo))
         if not overwrite:
             self.mat.vals.zero_()
         if self._err.shape[0] < len(plans):

@@ -447,6 +447,50 @@ def test_xfem_nitsche_compound(X, dim, fo):
     assert abs(got - got.T).max() <= 1e-11 * abs(ref).max()                  # the Nitsche form is symmetric
 
 
+def test_owner_partition_reproduces_single_rank(X):
+    """multi-GPU partition on one device: the rows each "rank" owns (ngsx_rowplan_create_owned over its element list incl.
+    halo) carry exactly the single-rank values -- owner-computes needs no interface-row exchange"""
+    from ngsxfem_b200 import partition
+    ngs, xf = X.ngs, X.xfem
+    mesh = ngs.Mesh(X.meshes.MakeStructured3DMesh(7))
+    gf = ngs.GridFunction(ngs.H1(mesh, order=1))
+    xf.InterpolateToP1(ngs.SphereLevelset((0.5, 0.5, 0.5), 0.35), gf)
+    ci = xf.CutInfo(mesh, gf)
+    hasneg = ci.GetElementsOfType(xf.HASNEG)
+    Vh = ngs.H1(mesh, order=2)
+    u, v = Vh.TnT()
+    form = ngs.grad(u) * ngs.grad(v) + u * v
+
+    def assemble(restr, owner):
+        a = xf.RestrictedBilinearForm(Vh, element_restriction=restr)
+        a.row_owner = owner
+        a += xf.SymbolicBFI(levelset_domain={"levelset": gf, "domain_type": NEG}, form=form, definedonelements=restr)
+        a.Assemble()
+        return a
+
+    full = assemble(hasneg, None)
+    rows_of = torch.repeat_interleave(torch.arange(Vh.ndof, device="cuda"), full.mat.rowptr[1:] - full.mat.rowptr[:-1])
+    active = hasneg.nonzero()
+    world = 3
+    owner = partition.row_owners(Vh.el2dof[active], Vh.ndof, world)
+    covered = torch.zeros(full.mat.nnz, dtype=torch.bool, device="cuda")
+    for r in range(world):
+        els = partition.elements_of_owner(Vh.el2dof, active, owner, r)
+        assert els.numel() < active.numel()
+        mine = torch.zeros(mesh.ne, dtype=torch.bool, device="cuda"); mine[els] = True
+        part = assemble(ngs.BitArray.from_bool(mine), (owner, r))
+        # the rank's restricted graph is a sub-pattern of the full one: compare through (row, col) keys
+        prow = torch.repeat_interleave(torch.arange(Vh.ndof, device="cuda"), part.mat.rowptr[1:] - part.mat.rowptr[:-1])
+        sel = owner[prow] == r
+        key_p = prow[sel] * Vh.ndof + part.mat.colidx[sel].long()
+        key_f = rows_of * Vh.ndof + full.mat.colidx.long()
+        pos = torch.searchsorted(key_f, key_p)
+        assert bool((key_f[pos] == key_p).all())
+        assert torch.equal(full.mat.vals[pos], part.mat.vals[sel])               # same pairs in the same order: bitwise equal
+        covered[pos] = True
+    assert bool(covered.all())
+
+
 def test_unsupported_paths_raise(X):
     mesh = X.ngs.Mesh(X.meshes.MakeStructured2DMesh(2))
     gf = X.ngs.GridFunction(X.ngs.H1(mesh, order=1))

@@ -43,6 +43,22 @@ def _worker(rank, world, port, out):
     if rank == 0:
         full, _ = orc.integrate_mesh(3, m.el2v.numpy(), m.vert.numpy(), ls.numpy(), 0, 4)
         out.put(dict(blocks=blocks, pairs=[int(x) for x in allp], total=int(d.numel()), sum=float(s), full=float(full), ndof=ndof))
+    # element-chunk ownership (the partition bench.py uses): every dof of an active element has exactly one owner, the rank's
+    # list holds its own chunk, and the lists of all ranks cover the active elements
+    owner = partition.row_owners(e2d[active], ndof, world)
+    touched = torch.zeros(ndof, dtype=torch.bool)
+    touched[e2d[active].reshape(-1).long()] = True
+    assert bool(((owner >= 0) == touched).all()) and int(owner.max()) == world - 1
+    mine_o = partition.elements_of_owner(e2d, active, owner, rank)
+    n = active.numel()
+    idx = torch.arange(n)
+    own_chunk = active[torch.div(idx * world, n, rounding_mode="floor") == rank]
+    assert bool(torch.isin(own_chunk, mine_o).all())
+    cnt = torch.tensor([int((owner == rank).sum()), mine_o.numel()], dtype=torch.int64)
+    allc = [torch.zeros_like(cnt) for _ in range(world)]
+    dist.all_gather(allc, cnt)
+    assert sum(int(c[0]) for c in allc) == int(touched.sum())
+    assert all(int(c[1]) <= 0.85 * n for c in allc)                                # a chunk + a halo layer, not everything
     # every element touching an owned row is listed, and nothing else
     touch = torch.zeros(m.ne, dtype=torch.bool)
     dd = e2d[active]
