@@ -67,11 +67,13 @@ typedef struct ngsx_mesh {
 /* bilinear form on scalar H1:  sum of
  *   c_stiff * h^hpow_stiff * grad(u).grad(v) + c_mass * h^hpow_mass * u v
  * + c_nitsche * h^hpow_nitsche * ( (grad(u).n) v + (grad(v).n) u ),   n = grad(lset_p1)/|grad(lset_p1)|,  h = |det J|^(1/dim)
+ * + c_dndn * h^hpow_dndn * (grad(u).n)(grad(v).n)      (c_stiff = -c_dndn: the tangential stiffness P grad(u).P grad(v),
+ *                                                       P = I - n n^T, of py_tutorials/tracefem3d.py:74-88)
  * (the coefficient functions of py_tutorials/fictdom_ghostpen.py:86-96; elementwise constant => evaluated once per element
  * like xfem/symboliccutbfi.cpp:205-214). */
 typedef struct ngsx_form_h1 {
-  double  c_mass, c_stiff, c_nitsche;
-  int32_t hpow_mass, hpow_stiff, hpow_nitsche, _pad;
+  double  c_mass, c_stiff, c_nitsche, c_dndn;
+  int32_t hpow_mass, hpow_stiff, hpow_nitsche, hpow_dndn;
 } ngsx_form_h1;
 
 /* polynomial coefficient function  f(x) = sum_{m<nterms} coef[m] * x^ex[m][0] * y^ex[m][1] * z^ex[m][2] */

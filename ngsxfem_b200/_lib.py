@@ -31,8 +31,8 @@ class Mesh(ctypes.Structure):
 
 
 class FormH1(ctypes.Structure):
-    _fields_ = [("c_mass", c_double), ("c_stiff", c_double), ("c_nitsche", c_double),
-                ("hpow_mass", c_i32), ("hpow_stiff", c_i32), ("hpow_nitsche", c_i32), ("_pad", c_i32)]
+    _fields_ = [("c_mass", c_double), ("c_stiff", c_double), ("c_nitsche", c_double), ("c_dndn", c_double),
+                ("hpow_mass", c_i32), ("hpow_stiff", c_i32), ("hpow_nitsche", c_i32), ("hpow_dndn", c_i32)]
 
 
 class XTerm(ctypes.Structure):

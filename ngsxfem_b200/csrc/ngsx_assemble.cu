@@ -24,7 +24,7 @@ namespace ngsx {
 constexpr int WARPS = 8;          // warps per CTA
 constexpr int QC = 16;            // quadrature points staged per round
 
-struct FormDev { double cm, cs, cn; int pm, ps, pn; };
+struct FormDev { double cm, cs, cn, cd; int pm, ps, pn, pd; };
 
 struct ElmatArgs {
   ngsx_mesh M;
@@ -177,10 +177,10 @@ __global__ void __launch_bounds__(WARPS * 32) k_elmat(ElmatArgs A, int64_t first
         ElGeom<DIM> G;
         element_geometry<DIM>(p, G);
         const double meas = fabs(G.det);
-        double cm = A.form.cm, cs = A.form.cs, cn = A.form.cn;
-        if (A.form.pm | A.form.ps | A.form.pn) {
+        double cm = A.form.cm, cs = A.form.cs, cn = A.form.cn, cd = A.form.cd;
+        if (A.form.pm | A.form.ps | A.form.pn | A.form.pd) {
           double h = DIM == 2 ? sqrt(meas) : cbrt(meas);           // specialcf.mesh_size = |det J|^(1/dim)
-          cm *= ipow(h, A.form.pm); cs *= ipow(h, A.form.ps); cn *= ipow(h, A.form.pn);
+          cm *= ipow(h, A.form.pm); cs *= ipow(h, A.form.ps); cn *= ipow(h, A.form.pn); cd *= ipow(h, A.form.pd);
         }
         if (!cut && fast) {
           // ---- constant-rule path -------------------------------------------------------------------------
@@ -267,10 +267,10 @@ __global__ void __launch_bounds__(WARPS * 32) k_elmat(ElmatArgs A, int64_t first
                   const double4 bi = stage[q * ND + ei[t]], bj = stage[q * ND + ej[t]];
                   double gg = bi.y * bj.y + bi.z * bj.z + (DIM == 3 ? bi.w * bj.w : 0.0);
                   double v = cs * gg + cm * bi.x * bj.x;
-                  if (cn != 0.0) {
+                  if (cn != 0.0 || cd != 0.0) {
                     double gin = bi.y * nrm[0] + bi.z * nrm[1] + (DIM == 3 ? bi.w * nrm[DIM - 1] : 0.0);
                     double gjn = bj.y * nrm[0] + bj.z * nrm[1] + (DIM == 3 ? bj.w * nrm[DIM - 1] : 0.0);
-                    v += cn * (gjn * bi.x + gin * bj.x);
+                    v += cn * (gjn * bi.x + gin * bj.x) + cd * gin * gjn;
                   }
                   acc[t] += f * v;
                 }
@@ -700,10 +700,10 @@ __global__ void __launch_bounds__(CUTMAT_THREADS) k_cutmat(ElmatArgs A, int64_t 
       ElGeom<DIM> G;
       element_geometry<DIM>(p, G);
       const double meas = fabs(G.det);
-      double cm = A.form.cm, cs = A.form.cs, cn = A.form.cn;
-      if (A.form.pm | A.form.ps | A.form.pn) {
+      double cm = A.form.cm, cs = A.form.cs, cn = A.form.cn, cd = A.form.cd;
+      if (A.form.pm | A.form.ps | A.form.pn | A.form.pd) {
         double h = DIM == 2 ? sqrt(meas) : cbrt(meas);
-        cm *= ipow(h, A.form.pm); cs *= ipow(h, A.form.ps); cn *= ipow(h, A.form.pn);
+        cm *= ipow(h, A.form.pm); cs *= ipow(h, A.form.ps); cn *= ipow(h, A.form.pn); cd *= ipow(h, A.form.pd);
       }
       double gl[DIM + 1][DIM];
       bary_gradients<DIM>(G, gl);
@@ -776,20 +776,21 @@ __global__ void __launch_bounds__(CUTMAT_THREADS) k_cutmat(ElmatArgs A, int64_t 
               for (int d = 0; d < DIM; d++) gv[i][d] = -0.5 * (gl[a][d] * lam[b] + lam[a] * gl[b][d]);
             }
           }
-          const double fs = f * cs, fm = f * cm, fn = f * cn;
+          const double fs = f * cs, fm = f * cm, fn = f * cn, fd = f * cd;
           int t = 0;
 #pragma unroll
           for (int i = 0; i < ND; i++) {
             double ag[DIM];
 #pragma unroll
             for (int d = 0; d < DIM; d++) ag[d] = fs * gv[i][d];
-            const double am = fm * sv[i] + fn * gn[i], an = fn * sv[i];     // (cm phi_i + cn dn phi_i) phi_j + cn phi_i dn phi_j
+            // (cm phi_i + cn dn phi_i) phi_j + (cn phi_i + cd dn phi_i) dn phi_j
+            const double am = fm * sv[i] + fn * gn[i], an = fn * sv[i] + fd * gn[i];
 #pragma unroll
             for (int j = 0; j <= i; j++) {
               double v = fma(am, sv[j], acc[t]);
 #pragma unroll
               for (int d = 0; d < DIM; d++) v = fma(ag[d], gv[j][d], v);
-              if (cn != 0.0) v = fma(an, gn[j], v);
+              if (cn != 0.0 || cd != 0.0) v = fma(an, gn[j], v);
               acc[t++] = v;
             }
           }
@@ -874,8 +875,8 @@ int ngsx_debug_get_timing(double *h_ms) {
 }
 
 static void fill_form(const ngsx_form_h1 *f, FormDev &d) {
-  d.cm = f->c_mass; d.cs = f->c_stiff; d.cn = f->c_nitsche;
-  d.pm = f->hpow_mass; d.ps = f->hpow_stiff; d.pn = f->hpow_nitsche;
+  d.cm = f->c_mass; d.cs = f->c_stiff; d.cn = f->c_nitsche; d.cd = f->c_dndn;
+  d.pm = f->hpow_mass; d.ps = f->hpow_stiff; d.pn = f->hpow_nitsche; d.pd = f->hpow_dndn;
 }
 
 int ngsx_elmat_h1(const ngsx_mesh *mesh, const double *lset_v, int fe_order, int dt, int intorder, const ngsx_form_h1 *h_form,
@@ -888,7 +889,7 @@ int ngsx_elmat_h1(const ngsx_mesh *mesh, const double *lset_v, int fe_order, int
   A.M = *mesh; A.lset = lset_v; A.tab = dd->cut_table; A.dt = dt;
   A.rule_vol = rv; A.nr_vol = nv; A.rule_if = ri; A.nr_if = ni;
   fill_form(h_form, A.form);
-  A.els = els; A.group = 1; A.use_fast = g_use_fast && h_form->c_nitsche == 0.0;
+  A.els = els; A.group = 1; A.use_fast = g_use_fast && h_form->c_nitsche == 0.0 && h_form->c_dndn == 0.0;
   A.elmats = elmats; A.npts = npts;
   return dispatch_elmat<0>(A, fe_order, dd->sm_count, 1, nullptr, nlist, as_stream(stream));
 }
@@ -905,7 +906,7 @@ int ngsx_assemble_csr_h1(const ngsx_mesh *mesh, const double *lset_v, int fe_ord
   A.M = *mesh; A.lset = lset_v; A.tab = dd->cut_table; A.dt = dt;
   A.rule_vol = rv; A.nr_vol = nv; A.rule_if = ri; A.nr_if = ni;
   fill_form(h_form, A.form);
-  A.els = els; A.group = group; A.use_fast = g_use_fast && h_form->c_nitsche == 0.0;
+  A.els = els; A.group = group; A.use_fast = g_use_fast && h_form->c_nitsche == 0.0 && h_form->c_dndn == 0.0;
   A.slots = slots; A.vals = vals;
   return dispatch_elmat<1>(A, fe_order, dd->sm_count, ncolors, h_color_ptr, nlist, as_stream(stream));
 }
@@ -929,7 +930,7 @@ int ngsx_assemble_csr_rows_h1(const ngsx_mesh *mesh, const double *lset_v, int f
   if (int rc = rows_scratch(plan, npairtab)) return rc;
   FormDev form;
   fill_form(h_form, form);
-  const int use_fast = g_use_fast && h_form->c_nitsche == 0.0 && dt != IF;
+  const int use_fast = g_use_fast && h_form->c_nitsche == 0.0 && h_form->c_dndn == 0.0 && dt != IF;
   // 1. reference tables (tiny), 2. geometry factors + quadrature work list, 3. cut-element matrices, 4. row gather
   if (g_timing) cudaEventRecord(g_ev[0], st);
   switch (dim * 10 + fe_order) {

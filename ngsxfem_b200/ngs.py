@@ -296,6 +296,8 @@ class Expr:
 
     @staticmethod
     def _contract(vec):
+        if list(vec) == ["n", "n"]:
+            return None                                # |n| = 1
         key = frozenset(vec)
         if key in Expr._CONTRACT:
             return Expr._CONTRACT[key]
@@ -320,7 +322,8 @@ class Expr:
                 atoms = list(a1 + a2)
                 vec = [a for a in atoms if a in Expr._VEC]
                 if len(vec) == 2:                      # NGSolve: vector * vector = inner product
-                    atoms = [a for a in atoms if a not in Expr._VEC] + [Expr._contract(vec)]
+                    c = Expr._contract(vec)
+                    atoms = [a for a in atoms if a not in Expr._VEC] + ([c] if c is not None else [])
                 elif len(vec) > 2:
                     raise _lib.NgsxError(-2, "unsupported vector product")
                 out.append((c1 * c2, p1 + p2, tuple(sorted(atoms))))

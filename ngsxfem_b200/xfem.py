@@ -249,9 +249,12 @@ class SymbolicCutBFI:
                 difforder_trial, difforder_test = 0, 0
             elif atoms in (("gun", "v"), ("gvn", "u")):
                 nit[atoms] = (c, p)
+            elif atoms == ("gun", "gvn"):                      # normal-normal part, e.g. of P(grad u).P(grad v), P = I - n n^T
+                f.c_dndn, f.hpow_dndn = c, p
+                difforder_trial, difforder_test = min(difforder_trial, 1), min(difforder_test, 1)
             else:
                 raise NgsxError(-2, f"form term {atoms} is outside the CUDA path (supported: grad(u)*grad(v), u*v, "
-                                    "(grad(u)*n)*v + (grad(v)*n)*u with n = LevelsetNormal()); no CPU fallback")
+                                    "(grad(u)*n)*v + (grad(v)*n)*u, (grad(u)*n)*(grad(v)*n) with n = LevelsetNormal()); no CPU fallback")
         if nit:
             if len(nit) != 2 or nit[("gun", "v")] != nit[("gvn", "u")]:
                 raise NgsxError(-2, "the Nitsche consistency terms must appear as the symmetric pair")

@@ -45,7 +45,8 @@ def test_no_oracle_in_product():
 def test_struct_layouts(lib):
     from ngsxfem_b200 import _lib
     assert ctypes.sizeof(_lib.Mesh) == 40
-    assert ctypes.sizeof(_lib.FormH1) == 40
+    assert ctypes.sizeof(_lib.FormH1) == 48
+    assert ctypes.sizeof(_lib.XTerm) == 32
     assert ctypes.sizeof(_lib.Poly) == 8 + 8 * 8 + 8 * 3 * 4
 
 

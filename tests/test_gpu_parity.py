@@ -447,6 +447,67 @@ def test_xfem_nitsche_compound(X, dim, fo):
     assert abs(got - got.T).max() <= 1e-11 * abs(ref).max()                  # the Nitsche form is symmetric
 
 
+@pytest.mark.parametrize("dim,fo", [(2, 1), (2, 2), (3, 1), (3, 2)])
+def test_tracefem_operator(X, dim, fo):
+    """config 4: TraceFEM Laplace-Beltrami operator, interface mass + tangential stiffness P grad(u).P grad(v), P = I - n n^T
+    (py_tutorials/tracefem3d.py:70-88) on the IF elements + ghost-penalty facet patches between IF elements; vs a numpy
+    evaluation on the oracle's interface rule and the oracle's patch matrices"""
+    from oracle import orc
+    import scipy.sparse as sp
+    ngs, xf = X.ngs, X.xfem
+    if dim == 2:
+        mesh = ngs.Mesh(X.meshes.MakeStructured2DMesh(8, lo=(-1.5, -1.5), hi=(1.5, 1.5)))
+        lset = ngs.SphereLevelset((0.03, -0.02), 1.0)
+    else:
+        mesh = ngs.Mesh(X.meshes.MakeStructured3DMesh(5))
+        lset = ngs.SphereLevelset((0.52, 0.49, 0.51), 0.36)
+    gf = ngs.GridFunction(ngs.H1(mesh, order=1))
+    xf.InterpolateToP1(lset, gf)
+    ci = xf.CutInfo(mesh, gf)
+    ba_if = ci.GetElementsOfType(IF)
+    ba_facets = xf.GetFacetsWithNeighborTypes(mesh, a=ba_if, b=ba_if)
+    Vh = ngs.H1(mesh, order=fo, dgjumps=True)
+    u, v = Vh.TnT()
+    n, h = ngs.LevelsetNormal(gf), ngs.specialcf.mesh_size
+    P = lambda w: w - (w * n) * n
+    a = xf.RestrictedBilinearForm(Vh, element_restriction=ba_if, facet_restriction=ba_facets)
+    a += xf.SymbolicBFI(levelset_domain={"levelset": gf, "domain_type": IF}, form=0.7 * P(ngs.grad(u)) * P(ngs.grad(v)) + 1.3 * u * v,
+                        definedonelements=ba_if)
+    a += xf.SymbolicFacetPatchBFI(form=0.1 * 1.0 / h * 1.0 / h * (u - u.Other()) * (v - v.Other()), skeleton=False, definedonelements=ba_facets)
+    assert a.integrators[0].intorder(fo) == 2 * fo
+    a.Assemble()
+    el2v, vert, ls, e2d = mesh.el2v.cpu().numpy(), mesh.vert.cpu().numpy(), gf.vec.cpu().numpy(), Vh.el2dof.cpu().numpy()
+    A = sp.lil_matrix((Vh.ndof, Vh.ndof))
+    for e in np.nonzero(ba_if.to_bool().cpu().numpy())[0]:
+        pm, l = vert[el2v[e]], ls[el2v[e]]
+        npt, pts, w = orc.cut_rule(dim, pm, l, IF, 2 * fo)
+        J = (pm[:dim] - pm[dim]).T
+        Jinv = np.linalg.inv(J); meas = abs(np.linalg.det(J))
+        gphi = Jinv.T @ (l[:dim] - l[dim]); nn = gphi / np.linalg.norm(gphi)
+        Pm = np.eye(dim) - np.outer(nn, nn)
+        em = np.zeros((Vh.nd, Vh.nd))
+        for q in range(npt):
+            sh, ds = orc.h1_shape(dim, fo, el2v[e], pts[q, :dim])
+            g = ds @ Jinv @ Pm
+            em += meas * w[q] * (0.7 * g @ g.T + 1.3 * np.outer(sh, sh))
+        d = e2d[e]
+        for i in range(len(d)):
+            for j in range(len(d)):
+                A[d[i], d[j]] += em[i, j]
+    f2e = mesh.facets()[1].cpu().numpy()
+    for fct in np.nonzero(ba_facets.to_bool().cpu().numpy())[0]:
+        e0, e1 = f2e[fct]
+        if e1 < 0:
+            continue
+        _, em = orc.facetpatch_elmat_h1(dim, fo, el2v[e0], vert[el2v[e0]], el2v[e1], vert[el2v[e1]], 0.1, -2)
+        d = np.concatenate([e2d[e0], e2d[e1]])
+        for i in range(len(d)):
+            for j in range(len(d)):
+                A[d[i], d[j]] += em[i, j]
+    ref = A.tocsr()
+    assert abs(a.mat.to_scipy() - ref).max() <= 1e-11 * abs(ref).max()
+
+
 def test_owner_partition_reproduces_single_rank(X):
     """multi-GPU partition on one device: the rows each "rank" owns (ngsx_rowplan_create_owned over its element list incl.
     halo) carry exactly the single-rank values -- owner-computes needs no interface-row exchange"""
