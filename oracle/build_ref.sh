@@ -3,7 +3,7 @@
 #
 # Builds oracle/_ref/libngsxref.so: the reference's OWN cut-quadrature / FE
 # sources compiled where they lie under /root/reference (ngsxfem
-# cutint/straightcutrule.cpp + the NGSolve fem / netgen ngcore files it needs),
+# cutint/straightcutrule.cpp, cutint/spacetimecutrule.cpp, spacetime/SpaceTimeFE.cpp + the NGSolve fem / netgen ngcore files they need),
 # plus our thin extern "C" driver oracle/ref_driver.cpp.  No reference source is
 # copied into this repository; outputs go to oracle/_ref/ only (git-ignored).
 #
@@ -86,7 +86,9 @@ for b in recursive_pol elementtopology finiteelement scalarfe intrule elementtra
          l2hofe l2hofe_segm l2hofe_trig l2hofe_tet; do
   FEM_OBJS+=("$OBJ/fem_$b.o"); par compile "$NGS/fem/$b.cpp" "$OBJ/fem_$b.o"
 done
-X_OBJS=("$OBJ/x_xdecompose.o" "$OBJ/x_straightcutrule.o")
+X_OBJS=("$OBJ/x_xdecompose.o" "$OBJ/x_straightcutrule.o" "$OBJ/x_SpaceTimeFE.o" "$OBJ/x_spacetimecutrule.o")
+par compile "$REF/spacetime/SpaceTimeFE.cpp" "$OBJ/x_SpaceTimeFE.o"
+par compile "$REF/cutint/spacetimecutrule.cpp" "$OBJ/x_spacetimecutrule.o"
 par compile "$REF/cutint/xdecompose.cpp" "$OBJ/x_xdecompose.o"
 par compile "$REF/cutint/straightcutrule.cpp" "$OBJ/x_straightcutrule.o"
 par compile "$HERE/ref_driver.cpp" "$OBJ/ref_driver.o"

@@ -316,6 +316,88 @@ int orc_cutinfo_element(int dim, const double *pmat, const double *ls, double *r
   return POS;
 }
 
+/* ------------------------------------------------------------------ space-time cut rule */
+/* cutint/spacetimecutrule.cpp:6-96 root_finding: zeros in (0,1) of the level-set trace of ONE vertex in time; nodal time element
+ * of order 0..2 (spacetime/SpaceTimeFE.cpp:150-160: nodes 0 | 0,1 | 0,1/2,1).  Same expressions as the reference, including
+ * the division by a = 0 when the order-2 data is linear in time (IEEE inf / nan -> no root). */
+static int st_roots(int ntd, const double *li, double *roots)
+{
+  int n = 0;
+  if (ntd == 2) {
+    if ((li[0] >= 0) != (li[1] >= 0)) roots[n++] = -li[0] / (li[1] - li[0]);
+  } else if (ntd == 3) {
+    double c = li[0], a = 2*li[0] + 2*li[2] - 4.*li[1], b = li[2] - a - c;
+    const double w = b*b - 4*a*c;
+    if (fabs(w) < 1e-12) {
+      double x = -b / (2*a);
+      if (x < 1 && x > 0) roots[n++] = x;
+    } else {
+      double x1 = (b + sqrt(w)) / (-2.0*a), x2 = (b - sqrt(w)) / (-2.0*a);
+      if (x1 < 1 && x1 > 0) roots[n++] = x1;
+      if (x2 < 1 && x2 > 0) roots[n++] = x2;
+    }
+  }
+  return n;
+}
+
+static void st_time_shape(int ntd, double t, double *sh)
+{
+  if (ntd == 1) sh[0] = 1.0;
+  else if (ntd == 2) { sh[0] = 1.0 - t; sh[1] = t; }
+  else { sh[0] = (1 - t) * (1 - 2*t) ; sh[1] = 4*t*(1 - t); sh[2] = t*(2*t - 1); }
+}
+
+/* cutint/spacetimecutrule.cpp:98-196 SpaceTimeCutIntegrationRule.  lset_st [ntd][dim+1] (time-major, SpaceTimeFESpace::GetDofNrs);
+ * out: spatial reference points, reference time per point, weights (wei_arr: w_space * w_time * (t1 - t0)).
+ * returns the number of points, ORC_NULL for an empty rule. */
+int orc_st_cut_rule(int dim, const double *pmat, const double *lset_st, int ntd, int dt, int order_time, int order_space,
+                    double *pts3, double *tq, double *wts, int cap)
+{
+  if (ntd < 1 || ntd > 3) return ORC_UNSUP;
+  const int nv = dim + 1;
+  double cp[16];
+  int ncp = 0;
+  cp[ncp++] = 0.0; cp[ncp++] = 1.0;
+  for (int i = 0; i < nv; i++) {
+    double li[3], r[2];
+    for (int k = 0; k < ntd; k++) li[k] = lset_st[k*nv + i];
+    int nr = st_roots(ntd, li, r);
+    for (int k = 0; k < nr; k++) cp[ncp++] = r[k];
+  }
+  for (int i = 1; i < ncp; i++) {                      /* sort (:121) */
+    double v = cp[i]; int j = i - 1;
+    while (j >= 0 && cp[j] > v) { cp[j+1] = cp[j]; j--; }
+    cp[j+1] = v;
+  }
+  const double (*rt)[4];
+  int nrt = select_rule(1, order_time, &rt);
+  if (nrt < 0) return nrt;
+  int n = 0;
+  for (int i = 0; i + 1 < ncp; i++) {
+    const double t0 = cp[i], t1 = cp[i+1];
+    for (int q = 0; q < nrt; q++) {
+      const double t = t0 + rt[q][0] * (t1 - t0);
+      double sh[3], ls[4];
+      st_time_shape(ntd, t, sh);
+      for (int v = 0; v < nv; v++) {
+        double d = 0;
+        for (int k = 0; k < ntd; k++) d += lset_st[k*nv + v] * sh[k];
+        if (fabs(d) < 1e-14) d = 1e-14;               /* :135 */
+        ls[v] = d;
+      }
+      int dom = orc_check_straight_cut(nv, ls);
+      int m = 0;
+      if (dom == IF) m = orc_cut_rule(dim, pmat, ls, dt, order_space, pts3 + 3*n, wts + n, cap - n);
+      else if (dom == dt) m = orc_select_rule(dim, order_space, pts3 + 3*n, wts + n, cap - n);
+      if (m == ORC_CAP || m == ORC_THROW || m == ORC_UNSUP) return m;
+      if (m < 0) m = 0;
+      for (int k = n; k < n + m; k++) { wts[k] = wts[k] * rt[q][3] * (t1 - t0); tq[k] = t; }
+      n += m;
+    }
+  }
+  return n == 0 ? ORC_NULL : n;
+}
+
 /* ------------------------------------------------------------------ H1 high-order shapes, orders 1..3 */
 /* NGS/fem/elementtopology.cpp:143-146 (trig edges), :161-167 (tet edges), faces :171-176 */
 static const int TRIG_EDGES[3][2] = {{2,0},{1,2},{0,1}};
@@ -514,6 +596,41 @@ double orc_integrate_mesh(int dim, int64_t ne, const int32_t *el2v, const double
     for (int q = 0; q < np; q++) {
       affine_map(&A, pts + 3*q, x);
       lsum += meas * w[q] * eval_mono(nmono, mono, x);
+    }
+    sum += lsum;
+    nptot += np;
+  }
+  if (npts_total) *npts_total = nptot;
+  return sum;
+}
+
+/* IntegrateX with time_order >= 0 (cutint/python_cutint.cpp:20-72 -> CreateCutIntegrationRule, cutint/xintegration.cpp:38-58):
+ * sum_e sum_q |det J_e| w_q f(x_q, t_q); mono rows {coef, ex, ey, ez, et} (et = power of the reference time tref).
+ * lset_st [ntd][nvtot] global space-time vector (dof = t * ndof_space + vertex, spacetime/SpaceTimeFESpace.cpp:109-122). */
+double orc_st_integrate_mesh(int dim, int64_t ne, const int32_t *el2v, const double *vert, int64_t nvtot, const double *lset_st, int ntd,
+                             int dt, int order_space, int order_time, int nmono, const double *mono5, int64_t *npts_total)
+{
+  double sum = 0;
+  int64_t nptot = 0;
+  const int nv = dim + 1;
+#pragma omp parallel for schedule(static) reduction(+:sum,nptot)
+  for (int64_t e = 0; e < ne; e++) {
+    static _Thread_local double pts[3*ORC_MAXPTS], w[ORC_MAXPTS], tq[ORC_MAXPTS];
+    double pmat[12], ls0[4], x[3], lst[12];
+    gather_el(dim, el2v, vert, lset_st, e, pmat, ls0, 0);
+    for (int k = 0; k < ntd; k++)
+      for (int v = 0; v < nv; v++) lst[k*nv + v] = lset_st[k*nvtot + el2v[e*nv + v]];
+    int np = orc_st_cut_rule(dim, pmat, lst, ntd, dt, order_time, order_space, pts, tq, w, ORC_MAXPTS);
+    if (np < 0) continue;
+    affine_t A;
+    affine_init(dim, pmat, &A);
+    double meas = fabs(A.det), lsum = 0;
+    for (int q = 0; q < np; q++) {
+      affine_map(&A, pts + 3*q, x);
+      double f = 0;
+      for (int m = 0; m < nmono; m++)
+        f += mono5[5*m] * pow(x[0], mono5[5*m+1]) * pow(x[1], mono5[5*m+2]) * pow(x[2], mono5[5*m+3]) * pow(tq[q], mono5[5*m+4]);
+      lsum += meas * w[q] * f;
     }
     sum += lsum;
     nptot += np;

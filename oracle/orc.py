@@ -41,6 +41,9 @@ def load():
     L.orc_cut_rule_untrafo.argtypes = [c_int, dp, c_int, c_int, dp, dp, c_int]
     L.orc_cut_rule.argtypes = [c_int, dp, dp, c_int, c_int, dp, dp, c_int]
     L.orc_cutinfo_element.argtypes = [c_int, dp, dp, dp]
+    L.orc_st_cut_rule.argtypes = [c_int, dp, dp, c_int, c_int, c_int, c_int, dp, dp, dp, c_int]
+    L.orc_st_integrate_mesh.argtypes = [c_int, c_i64, ip, dp, c_i64, dp, c_int, c_int, c_int, c_int, c_int, dp, lp]
+    L.orc_st_integrate_mesh.restype = c_double
     L.orc_h1_ndof.argtypes = [c_int, c_int]
     L.orc_h1_shape.argtypes = [c_int, c_int, ip, dp, dp, dp]
     L.orc_elmat_h1.argtypes = [c_int, c_int, ip, dp, dp, c_int, c_int, c_double, c_double, dp]
@@ -111,6 +114,32 @@ def cut_rule(dim, pmat, lset, dt, order, impl="oracle", cap=2048):
     if n < 0:
         return n, None, None
     return n, pts[:n].copy(), w[:n].copy()
+
+
+def st_cut_rule(dim, pmat, lset_st, dt, order_time, order_space, impl="oracle", cap=4096):
+    """space-time cut rule of one element: lset_st [ntd][dim+1].  returns (n, pts, tref, weights)"""
+    pts = np.zeros((cap, 3)); tq = np.zeros(cap); w = np.zeros(cap)
+    ls = _d(lset_st); pm = _d(pmat)
+    ntd = ls.shape[0]
+    if impl == "oracle":
+        n = load().orc_st_cut_rule(dim, P(pm), P(ls), ntd, dt, order_time, order_space, P(pts), P(tq), P(w), cap)
+    else:
+        from . import refload
+        n = refload.load().ref_st_cut_rule(ET[dim], P(pm), P(ls), ntd, dt, order_time, order_space, P(pts), P(tq), P(w), cap)
+    if n < 0:
+        return n, None, None, None
+    return n, pts[:n].copy(), tq[:n].copy(), w[:n].copy()
+
+
+def st_integrate_mesh(dim, el2v, vert, lset_st, dt, order_space, order_time, mono5=None, nthreads=0):
+    """IntegrateX(..., time_order=order_time): lset_st [ntd][nv]; mono5 rows (coef, ex, ey, ez, et)"""
+    el2v = _i(el2v); vert = _d(vert); ls = _d(lset_st)
+    mo = _d(np.array([[1.0, 0, 0, 0, 0]] if mono5 is None else mono5, dtype=np.float64).reshape(-1, 5))
+    npt = c_i64(0)
+    load().orc_set_threads(nthreads)
+    v = load().orc_st_integrate_mesh(dim, el2v.shape[0], P(el2v, ip), P(vert), vert.shape[0], P(ls), ls.shape[0], dt, order_space, order_time,
+                                     mo.shape[0], P(mo), ctypes.byref(npt))
+    return v, npt.value
 
 
 def cutinfo_element(dim, pmat, lset, impl="oracle"):

@@ -8,6 +8,7 @@
 //   * ngfem::SelectIntegrationRule                              (NGS/fem/intrule.cpp:2620-2659)
 //   * ngfem::H1HighOrderFE<ET>::CalcShape / CalcMappedDShape    (NGS/fem/h1hofe_impl.hpp)
 //   * ngfem::FE_ElementTransformation / MappedIntegrationRule   (NGS/fem/elementtransformation.cpp)
+//   * xintegration::SpaceTimeCutIntegrationRule + ngfem::NodalTimeFE (cutint/spacetimecutrule.cpp:98-196, spacetime/SpaceTimeFE.cpp:116-173)
 //   * ngbla::AddABt                                             (NGS/basiclinalg/ngblas.cpp)
 // The only restated logic is the ~30-line B*D*B^T accumulation of
 // xfem/symboliccutbfi.cpp:219-301 (diagonal-proxy branch; the symbolic
@@ -16,6 +17,8 @@
 // xfem/cutinfo.cpp:79-111.
 #include <fem.hpp>
 #include "../cutint/straightcutrule.hpp"
+#include "../cutint/spacetimecutrule.hpp"
+#include "../spacetime/SpaceTimeFE.hpp"
 #include <omp.h>
 
 using namespace ngfem;
@@ -180,6 +183,42 @@ int ref_cut_rule(int et, const double * pmat, const double * lset, int dt, int o
     else if (et == ET_TET) { FE_ElementTransformation<3,3> * t; ir = TrafoRule<3>(ET_TET, pmat, lset, dt, order, lh, t); }
     else return -4;
     return CopyRule(ir, pts3, wts, cap);
+  } catch (...) { return -2; }
+}
+
+// cutint/spacetimecutrule.cpp:98-196 with the nodal time element of order ntdofs - 1 (spacetime/SpaceTimeFE.cpp:116-173).
+// lset_st [ntdofs][nv]: time-major like SpaceTimeFESpace::GetDofNrs (spacetime/SpaceTimeFESpace.cpp:109-122).
+// out: spatial reference points, reference time of each point (the reference smuggles it through Weight()), weights (wei_arr)
+int ref_st_cut_rule(int et, const double * pmat, const double * lset_st, int ntdofs, int dt, int order_time, int order_space,
+                    double * pts3, double * tq, double * wts, int cap)
+{
+  LocalHeap & lh = GetLH(); HeapReset hr(lh);
+  try {
+    if (et != ET_TRIG && et != ET_TET) return -4;
+    const int D = et == ET_TRIG ? 2 : 3, nv = D + 1;
+    Vector<> lv(ntdofs * nv);
+    for (int i = 0; i < ntdofs * nv; i++) lv(i) = lset_st[i];
+    NodalTimeFE tfe(ntdofs - 1, false, false);
+    const IntegrationRule * ir = nullptr;
+    Array<double> wei;
+    Matrix<> pm(nv, D);
+    for (int i = 0; i < nv; i++) for (int d = 0; d < D; d++) pm(i,d) = pmat[i*D+d];
+    if (D == 2) {
+      auto trafo = new (lh) FE_ElementTransformation<2,2>(ET_TRIG, pm);
+      tie(ir, wei) = SpaceTimeCutIntegrationRule(lv, *trafo, &tfe, DOMAIN_TYPE(dt), order_time, order_space, FIND_OPTIMAL, lh);
+    } else {
+      auto trafo = new (lh) FE_ElementTransformation<3,3>(ET_TET, pm);
+      tie(ir, wei) = SpaceTimeCutIntegrationRule(lv, *trafo, &tfe, DOMAIN_TYPE(dt), order_time, order_space, FIND_OPTIMAL, lh);
+    }
+    if (!ir) return -1;
+    const int n = ir->Size();
+    if (n > cap) return -3;
+    for (int i = 0; i < n; i++) {
+      for (int d = 0; d < 3; d++) pts3[3*i+d] = (*ir)[i](d);
+      tq[i] = (*ir)[i].Weight();
+      wts[i] = wei[i];
+    }
+    return n;
   } catch (...) { return -2; }
 }
 

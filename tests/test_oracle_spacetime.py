@@ -1,0 +1,69 @@
+"""Space-time cut rule: the C restatement (oracle/ngsx_oracle.c:orc_st_cut_rule) against
+  (a) the reference's own spacetimecutrule.cpp + NodalTimeFE compiled in place (oracle/_ref), on randomised elements,
+  (b) the reference's known-answer tests tests/pytests/test_spacetimecutrule.py:12-68 restated without NGSolve."""
+import numpy as np
+import pytest
+
+from oracle import orc, refload
+
+NEG, POS, IF = 0, 1, 2
+needs_ref = pytest.mark.skipif(not refload.available(), reason="compiled reference (oracle/_ref) not built")
+
+
+def _rand_element(rng, dim):
+    pm = rng.uniform(-1, 1, size=(dim + 1, dim))
+    while abs(np.linalg.det((pm[:dim] - pm[dim]).T)) < 0.05:
+        pm = rng.uniform(-1, 1, size=(dim + 1, dim))
+    return pm
+
+
+@needs_ref
+@pytest.mark.parametrize("dim", [2, 3])
+@pytest.mark.parametrize("ntd", [1, 2, 3])
+def test_st_rule_vs_compiled_reference(dim, ntd):
+    rng = np.random.default_rng(20241104 + 10 * dim + ntd)
+    ncut = 0
+    for trial in range(120):
+        pm = _rand_element(rng, dim)
+        ls = rng.uniform(-1, 1, size=(ntd, dim + 1)) + rng.uniform(-0.6, 0.6)
+        if trial % 7 == 0 and ntd == 3:
+            ls[1] = 0.5 * (ls[0] + ls[2])                 # linear in time on an order-2 time element: the reference's a == 0 branch
+        for dt in (NEG, POS, IF):
+            for ot, os_ in ((0, 0), (2, 2), (4, 3)):
+                n1, p1, t1, w1 = orc.st_cut_rule(dim, pm, ls, dt, ot, os_)
+                n2, p2, t2, w2 = orc.st_cut_rule(dim, pm, ls, dt, ot, os_, impl="ref")
+                assert max(n1, 0) == max(n2, 0), (trial, dt, ot, os_)
+                if n1 > 0:
+                    ncut += 1
+                    assert np.array_equal(t1, t2) or np.abs(t1 - t2).max() < 1e-14
+                    assert np.abs(p1 - p2).max() < 1e-12
+                    assert np.abs(w1 - w2).max() <= 1e-12 * max(np.abs(w2).max(), 1e-300)
+    assert ncut > 200
+
+
+def _unit_square():
+    vert = np.array([[0, 0], [1, 0], [0, 1], [1, 1]], dtype=float)
+    el2v = np.array([[0, 1, 2], [3, 2, 1]], dtype=np.int32)                  # NGS/python/meshes.py:109-117 (nx = ny = 1)
+    return vert, el2v
+
+
+@pytest.mark.parametrize("mono,ref,os_,ot", [([[1, 0, 0, 0, 1]], 0.5, 0, 1),
+                                             ([[1, 0, 0, 0, 3]], 0.25, 0, 3),
+                                             ([[1, 0, 0, 0, 0], [-3, 0, 0, 0, 1], [3, 0, 0, 0, 2], [-1, 0, 0, 0, 3]], 0.25, 0, 3),
+                                             ([[1, 1, 0, 0, 0]], 0.5, 1, 0),
+                                             ([[1, 2, 0, 0, 2], [1, 0, 2, 0, 2]], 2 / 9, 2, 2)])
+def test_spacetime_integrate_no_cut(mono, ref, os_, ot):
+    """tests/pytests/test_spacetimecutrule.py:12-36 (triangles): tref, tref^3, (1-tref)^3, x, tref^2 (x^2+y^2) on the unit square"""
+    vert, el2v = _unit_square()
+    ls = -np.ones((2, 4))
+    val, _ = orc.st_integrate_mesh(2, el2v, vert, ls, NEG, os_, ot, mono)
+    assert abs(val - ref) < 5e-15
+
+
+@pytest.mark.parametrize("dt,ref", [(POS, 1 / 8), (NEG, 7 / 8), (IF, 1 / 2)])
+def test_spacetime_straight_cut_2Dplus1D(dt, ref):
+    """tests/pytests/test_spacetimecutrule.py:39-68: level set 1 - 2x - 2t, order = time_order = 0"""
+    vert, el2v = _unit_square()
+    ls = np.array([1 - 2 * vert[:, 0], 1 - 2 * vert[:, 0] - 2])
+    val, _ = orc.st_integrate_mesh(2, el2v, vert, ls, dt, 0, 0)
+    assert abs(val - ref) < 5e-15
