@@ -19,6 +19,8 @@
  *   ngsx_assemble_csr_h1      NGS/comp/bilinearform.cpp:1117-1575 + NGS/linalg/sparsematrix_impl.hpp:63-103
  *   ngsx_assemble_vec_h1      NGS/comp/linearform.cpp:209-243
  *   ngsx_integrate            cutint/python_cutint.cpp:20-72        (IntegrateX)
+ *   ngsx_st_rule_count/_fill, ngsx_st_integrate
+ *                             cutint/spacetimecutrule.cpp:6-196, cutint/xintegration.cpp:38-58 (time_order >= 0)
  *   ngsx_facets_neighbor_types, ngsx_elements_with_neighbor_facets, ngsx_dofs_of_elements
  *                             xfem/cutinfo.cpp:191-304              (xfem/python_xfem.cpp:168-318)
  *   ngsx_facetpatch_elmat_h1, ngsx_facetpatch_cmat_h1
@@ -206,6 +208,23 @@ int ngsx_assemble_csr_rows_mats(ngsx_rowplan *plan, const double *mats, int accu
 /* out[0] = sum_e sum_q |det J_e| w_q f(x_q) over the (dt, order) cut rule; fixed-shape tree reduction (bitwise
  * reproducible run to run).  out is a device double. */
 int ngsx_integrate(const ngsx_mesh *mesh, const double *lset_v, int dt, int order, const ngsx_poly *h_f, double *out, void *stream);
+
+/* ---- (f-3) space-time cut quadrature -----------------------------------------------------------------------------
+ * SpaceTimeCutIntegrationRule (cutint/spacetimecutrule.cpp:98-196) for a level set that is P1 in space and nodal of order
+ * ntime_dofs - 1 (0..2) in the reference time: lset_st [ntime_dofs][nv], time-major like SpaceTimeFESpace::GetDofNrs
+ * (spacetime/SpaceTimeFESpace.cpp:109-122).  npts[e] = size of the element's space-time rule (0 where the reference returns
+ * nullptr); points (reference coordinates), reference times and weights (the reference's wei_arr: w_space * w_time * (t1-t0),
+ * IF weights carry |F^-T n|) are written at offs[e] in the reference's emission order.  Time elements of order > 2 (bisection
+ * root finding, spacetimecutrule.cpp:46-95) are NGSX_ERR_UNSUPPORTED. */
+int ngsx_st_rule_count(const ngsx_mesh *mesh, const double *lset_st, int ntime_dofs, int dt, int order_space, int order_time,
+                       int32_t *npts, void *stream);
+int ngsx_st_rule_fill(const ngsx_mesh *mesh, const double *lset_st, int ntime_dofs, int dt, int order_space, int order_time,
+                      const int64_t *offs, double *pts3, double *tref, double *wts, void *stream);
+/* IntegrateX with time_order >= 0 (cutint/python_cutint.cpp:20-72): out[0] = sum_e sum_q |det J_e| w_q f(x_q, tref_q),
+ * f = sum_m coef[m] x^ex[m][0] y^ex[m][1] z^ex[m][2] tref^h_texp[m] (h_texp: host array [nterms] or NULL = no time dependence);
+ * fixed-shape reduction, bitwise reproducible. */
+int ngsx_st_integrate(const ngsx_mesh *mesh, const double *lset_st, int ntime_dofs, int dt, int order_space, int order_time,
+                      const ngsx_poly *h_f, const int32_t *h_texp, double *out, void *stream);
 
 /* ---- facet / element / dof marking ----------------------------------------------------------------------------- */
 /* facet2el [nf][2], -1 = no neighbour (boundary facet: bnd_val_a/b are used, xfem/cutinfo.cpp:238-241) */

@@ -219,6 +219,69 @@ class Poly:
 x, y, z = Poly({(1, 0, 0): 1.0}), Poly({(0, 1, 0): 1.0}), Poly({(0, 0, 1): 1.0})
 
 
+class TPoly:
+    """polynomial in x, y, z and the reference time tref (ReferenceTimeVariable of the reference's space-time module):
+    {(ex, ey, ez, et): coef}"""
+
+    def __init__(self, terms):
+        self.terms = {k: float(v) for k, v in terms.items() if v != 0.0}
+
+    @staticmethod
+    def lift(o):
+        if isinstance(o, TPoly):
+            return o
+        p = Poly.lift(o)
+        return None if p is None else TPoly({(*k, 0): v for k, v in p.terms.items()})
+
+    def __add__(self, o):
+        o = TPoly.lift(o)
+        if o is None:
+            return NotImplemented
+        t = dict(self.terms)
+        for k, v in o.terms.items():
+            t[k] = t.get(k, 0.0) + v
+        return TPoly(t)
+
+    __radd__ = __add__
+
+    def __neg__(self):
+        return TPoly({k: -v for k, v in self.terms.items()})
+
+    def __sub__(self, o):
+        o = TPoly.lift(o)
+        return NotImplemented if o is None else self + (-o)
+
+    def __rsub__(self, o):
+        return (-self) + o
+
+    def __mul__(self, o):
+        o = TPoly.lift(o)
+        if o is None:
+            return NotImplemented
+        t = {}
+        for k1, v in self.terms.items():
+            for k2, w in o.terms.items():
+                k = tuple(a + b for a, b in zip(k1, k2))
+                t[k] = t.get(k, 0.0) + v * w
+        return TPoly(t)
+
+    __rmul__ = __mul__
+
+    def __pow__(self, n):
+        r = TPoly({(0, 0, 0, 0): 1.0})
+        for _ in range(int(n)):
+            r = r * self
+        return r
+
+    def as_terms(self):
+        return [(c, *k) for k, c in sorted(self.terms.items())] or [(0.0, 0, 0, 0, 0)]
+
+
+def ReferenceTimeVariable():
+    """tref of the reference (spacetime/python_spacetime.cpp): the reference time in [0, 1] of a space-time quadrature point"""
+    return TPoly({(0, 0, 0, 1): 1.0})
+
+
 def CoefficientFunction(v):
     return Poly.lift(v)
 

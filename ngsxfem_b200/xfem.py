@@ -184,8 +184,11 @@ def _poly_of(cf):
 def IntegrateX(lset, mesh: Mesh, cf=None, order: int = 5, domain_type=IF, subdivlvl: int = 0, time_order: int = -1,
                quad_dir_policy=OPTIMAL, heapsize: int = 1000000, sync: bool = True):
     """cutint/python_cutint.cpp:20-72.  Deterministic tree reduction on the device (the reference's AtomicAdd order is not)."""
-    if subdivlvl != 0 or time_order >= 0:
-        raise NgsxError(-2, "subdivlvl > 0 / space-time integration is outside the CUDA path")
+    if subdivlvl != 0:
+        raise NgsxError(-2, "subdivlvl > 0 (legacy integration) is outside the CUDA path")
+    if time_order >= 0:                                              # space-time rule (cutint/xintegration.cpp:38-58)
+        from . import spacetime
+        return spacetime.integrate(lset, mesh, cf, order, domain_type, time_order, sync)
     lv = _lset_vec(lset)
     out = torch.zeros(1, dtype=torch.float64, device=mesh.device)
     poly = _poly_of(cf)
@@ -729,3 +732,5 @@ class LinearForm:
 
 # XFESpace and the sign-masked operators (xfem/python_xfem.cpp:321-448, python/__init__.py:22-105, 397-409)
 from .xfes import XFESpace, CutRatioGF, neg, pos, neg_grad, pos_grad, extend, extend_grad  # noqa: E402,F401
+from .spacetime import ScalarTimeFE, SpaceTimeFESpace, SpaceTimeInterpolateToP1  # noqa: E402,F401
+from .ngs import ReferenceTimeVariable  # noqa: E402,F401

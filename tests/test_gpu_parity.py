@@ -508,6 +508,86 @@ def test_tracefem_operator(X, dim, fo):
     assert abs(a.mat.to_scipy() - ref).max() <= 1e-11 * abs(ref).max()
 
 
+@pytest.mark.parametrize("dim", [2, 3])
+@pytest.mark.parametrize("tord", [0, 1, 2])
+def test_spacetime_rule_vs_oracle(X, dim, tord):
+    """f-3: batched space-time cut rule (counts bit-exact, points / times / weights to 1e-12) and space-time Integrate vs the
+    oracle's restatement of cutint/spacetimecutrule.cpp:98-196 (itself pinned against the compiled reference)"""
+    from oracle import orc
+    from ngsxfem_b200 import spacetime
+    ngs, xf = X.ngs, X.xfem
+    mesh = ngs.Mesh(X.meshes.MakeStructured2DMesh(7) if dim == 2 else X.meshes.MakeStructured3DMesh(3))
+    fes = xf.SpaceTimeFESpace(ngs.H1(mesh, order=1), xf.ScalarTimeFE(tord))
+    gf = ngs.GridFunction(fes)
+    c = (0.45, 0.5, 0.55)[:dim]
+
+    def lset(*a):
+        *xs, t = a
+        r2 = sum((xs[d] - c[d] - (0.25 * t if d == 0 else 0.1 * t * t)) ** 2 for d in range(dim))
+        return torch.sqrt(r2) - 0.3
+    xf.SpaceTimeInterpolateToP1(lset, None, gf)
+    if tord == 2:
+        gf.vec[mesh.nv:2 * mesh.nv][::5] = 0.5 * (gf.vec[:mesh.nv][::5] + gf.vec[2 * mesh.nv:][::5])     # exercise the a == 0 branch
+    el2v, vert = mesh.el2v.cpu().numpy(), mesh.vert.cpu().numpy()
+    ls = gf.vec.cpu().numpy().reshape(tord + 1, mesh.nv)
+    tref = xf.ReferenceTimeVariable()
+    for dt in (NEG, POS, IF):
+        for os_, ot in ((0, 0), (2, 2), (4, 3)):
+            npts, offs, pts, tq, w = spacetime.cut_rule(gf, mesh, dt, os_, ot)
+            npts, offs, pts, tq, w = (a.cpu().numpy() for a in (npts, offs, pts, tq, w))
+            for e in range(mesh.ne):
+                n, p_o, t_o, w_o = orc.st_cut_rule(dim, vert[el2v[e]], ls[:, el2v[e]], dt, ot, os_)
+                assert max(n, 0) == npts[e], (e, dt, os_, ot)
+                if n > 0:
+                    sl = slice(offs[e], offs[e] + n)
+                    assert np.abs(pts[sl] - p_o).max() < 1e-12 and np.abs(tq[sl] - t_o).max() < 1e-13
+                    assert np.abs(w[sl] - w_o).max() <= 1e-12 * np.abs(w_o).max()
+            mono = [[1.0, 0, 0, 0, 0], [0.5, 1, 0, 0, 2], [-0.25, 0, 2, 0, 1]]
+            ref, _ = orc.st_integrate_mesh(dim, el2v, vert, ls, dt, os_, ot, mono)
+            got = xf.Integrate(levelset_domain={"levelset": gf, "domain_type": dt}, cf=1.0 + 0.5 * ngs.x * tref ** 2 - 0.25 * ngs.y ** 2 * tref,
+                               mesh=mesh, order=os_, time_order=ot)
+            assert abs(got - ref) <= 1e-12 * max(abs(ref), 1e-3)
+            assert got == xf.Integrate(levelset_domain={"levelset": gf, "domain_type": dt},
+                                       cf=1.0 + 0.5 * ngs.x * tref ** 2 - 0.25 * ngs.y ** 2 * tref, mesh=mesh, order=os_, time_order=ot)
+
+
+def test_spacetime_reference_kats_and_scale(X):
+    """tests/pytests/test_spacetimecutrule.py:12-68 on the GPU + config 5 (2D+t moving circle, ~2 M triangles, order 2 x 2):
+    NEG + POS = |Omega| x 1, space-time volume of the moving disc, interface measure integrated in time"""
+    from math import pi
+    ngs, xf = X.ngs, X.xfem
+    tref = xf.ReferenceTimeVariable()
+    x, y = ngs.x, ngs.y
+    mesh = ngs.Mesh(X.meshes.MakeStructured2DMesh(1))
+    fes = xf.SpaceTimeFESpace(ngs.H1(mesh, order=1), xf.ScalarTimeFE(1))
+    gf = ngs.GridFunction(fes)
+    gf.vec[:] = -1
+    for f, ref, os_, ot in ((tref, 0.5, 0, 1), (tref ** 3, 0.25, 0, 3), ((1 - tref) ** 3, 0.25, 0, 3), (x, 0.5, 1, 0),
+                            (tref * tref * (x * x + y * y), 2 / 9, 2, 2)):
+        val = xf.Integrate(levelset_domain={"levelset": gf, "domain_type": NEG}, cf=f, mesh=mesh, order=os_, time_order=ot)
+        assert abs(val - ref) < 5e-15
+    xf.SpaceTimeInterpolateToP1(1 - 2 * x - 2 * tref, tref, gf)
+    for dt, ref in ((POS, 1 / 8), (NEG, 7 / 8), (IF, 1 / 2)):
+        val = xf.Integrate(levelset_domain={"levelset": gf, "domain_type": dt}, cf=1.0, mesh=mesh, order=0, time_order=0)
+        assert abs(val - ref) < 5e-15
+    with pytest.raises(X.lib.NgsxError):
+        xf.ScalarTimeFE(3)
+    # config 5
+    nx = 1000
+    mesh = ngs.Mesh(X.meshes.MakeStructured2DMesh(nx, device="cuda"))
+    fes = xf.SpaceTimeFESpace(ngs.H1(mesh, order=1), xf.ScalarTimeFE(2))
+    gf = ngs.GridFunction(fes)
+    r0 = 0.25
+    xf.SpaceTimeInterpolateToP1(lambda xx, yy, t: torch.sqrt((xx - 0.35 - 0.3 * t) ** 2 + (yy - 0.5) ** 2) - r0, None, gf)
+    ld = lambda dt: {"levelset": gf, "domain_type": dt}
+    vneg = xf.Integrate(levelset_domain=ld(NEG), cf=1.0, mesh=mesh, order=2, time_order=2)
+    vpos = xf.Integrate(levelset_domain=ld(POS), cf=1.0, mesh=mesh, order=2, time_order=2)
+    vif = xf.Integrate(levelset_domain=ld(IF), cf=1.0, mesh=mesh, order=2, time_order=2)
+    assert abs(vneg + vpos - 1.0) < 1e-11
+    assert abs(vneg - pi * r0 ** 2) < 1e-3 and abs(vif - 2 * pi * r0) < 5e-3        # quadratic-in-time interpolation of the moving level set
+    assert vneg == xf.Integrate(levelset_domain=ld(NEG), cf=1.0, mesh=mesh, order=2, time_order=2)
+
+
 def test_owner_partition_reproduces_single_rank(X):
     """multi-GPU partition on one device: the rows each "rank" owns (ngsx_rowplan_create_owned over its element list incl.
     halo) carry exactly the single-rank values -- owner-computes needs no interface-row exchange"""
