@@ -621,16 +621,26 @@ class BilinearForm:
                                              plan.group, _ptr(self.mat.vals), _stream()))
         return self
 
-    def check_degenerate(self):
-        """raise if the last Assemble met a level set the reference throws on; synchronises"""
-        if not self._err_armed:
-            return
-        self._err_armed = False
-        err = self._err.tolist()
+    def check_degenerate(self, err=None):
+        """raise if the last Assemble met a level set the reference throws on; synchronises.
+        err: host copy of degenerate_flags() the caller downloaded itself (pipelined callers: no synchronisation here)"""
+        if err is None:
+            if not self._err_armed:
+                return
+            self._err_armed = False
+            err = self._err.tolist()
+        else:
+            err = err.tolist()
         n, first = sum(r[0] for r in err), min(r[1] for r in err)
         if n:
             raise NgsxError(-4, f"{n} element(s) carry a level set the reference rejects (first: element {first}): "
                                 "'You tried to cut a simplex with a plain geometry lset function'")
+
+    def degenerate_flags(self):
+        """device tensor [{count, first element}] per integrator of the last Assemble, for callers that download it on their
+        own stream together with the values and hand the host copy to check_degenerate(err)"""
+        self._err_armed = False
+        return self._err
 
     def _assemble_x(self, integ, plan, k):
         """compound integrator: Vh part on the uncut elements through the H1 row gather, then the (2 nd)^2 blocks of the IF elements
