@@ -810,10 +810,192 @@ __global__ void __launch_bounds__(CUTMAT_THREADS) k_cutmat(ElmatArgs A, int64_t 
   }
 }
 
+// ---------------------------------------------------------------------------------------------------------------
+// Same matrices from MONOMIAL MOMENTS (forms without normal-derivative terms).  The hierarchical shapes are lam_i and
+// -1/2 lam_a lam_b, their barycentric derivatives are constants and -1/2 lam, so every entry of the mass and stiffness
+// block is a fixed combination of int lam^alpha over the cut part: per rule point the thread accumulates the moments
+// (3D P2: 1 + 4 + 10 + 24 + 21 = 60 accumulators, 76 FP64 instructions) instead of the 55 x 4 entry updates plus the
+// shape / gradient evaluation (~ 340), and expands them into the nd x nd block once per element.  Same rule, same points
+// and weights; only the summation order differs (1e-15 relative).
+// ---------------------------------------------------------------------------------------------------------------
+__device__ __forceinline__ constexpr int sym2(int a, int b) { return a >= b ? a * (a + 1) / 2 + b : b * (b + 1) / 2 + a; }
+
+template <int DIM, int ORDER, bool IFACE>
+__global__ void __launch_bounds__(CUTMAT_THREADS) k_cutmat_mom(ElmatArgs A, int64_t count) {
+  constexpr int ND = H1<DIM, ORDER>::ND, NE = ND * ND, NV = DIM + 1, NEDGE = ND - NV;
+  constexpr int N2 = NV * (NV + 1) / 2, NT = NEDGE > 0 ? NEDGE : 1, NQ = NEDGE > 0 ? NEDGE * (NEDGE + 1) / 2 : 1;
+  constexpr int NPT = IFACE ? DIM : DIM + 1;
+  extern __shared__ __align__(16) unsigned char smem_raw[];
+  double4 *srule_vol = reinterpret_cast<double4 *>(smem_raw);
+  double4 *srule_if = srule_vol + A.nr_vol;
+  CutEntry *lut = reinterpret_cast<CutEntry *>(srule_if + A.nr_if);
+  for (int i = threadIdx.x; i < A.nr_vol; i += blockDim.x) srule_vol[i] = A.rule_vol[i];
+  for (int i = threadIdx.x; i < A.nr_if; i += blockDim.x) srule_if[i] = A.rule_if[i];
+  if (threadIdx.x < 16) lut[threadIdx.x] = A.tab->e[DIM - 2][A.dt][threadIdx.x];
+  __syncthreads();
+  if (A.d_count) count = *A.d_count;
+  for (int64_t s = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; s < count; s += (int64_t)gridDim.x * blockDim.x) {
+    const int64_t kk = A.sublist ? A.sublist[s] : s;
+    const int64_t e = A.els ? A.els[kk] : kk;
+    double ls[4], p[DIM + 1][DIM];
+    load_el<DIM>(A.M, A.lset, e, ls, p);
+    int mask;
+    const int dom = sign_test<DIM>(ls, mask);
+    const bool cut = dom == IF;
+    double m0 = 0.0, m1[NV], m2[N2], mT[NV][NT], mQ[NQ];
+#pragma unroll
+    for (int a = 0; a < NV; a++) {
+      m1[a] = 0.0;
+#pragma unroll
+      for (int t = 0; t < NT; t++) mT[a][t] = 0.0;
+    }
+#pragma unroll
+    for (int t = 0; t < N2; t++) m2[t] = 0.0;
+#pragma unroll
+    for (int t = 0; t < NQ; t++) mQ[t] = 0.0;
+    double cm = A.form.cm, cs = A.form.cs;
+    double gl[DIM + 1][DIM];
+#pragma unroll
+    for (int k = 0; k <= DIM; k++)
+#pragma unroll
+      for (int d = 0; d < DIM; d++) gl[k][d] = 0.0;
+    if (cut || dom == A.dt) {
+      ElGeom<DIM> G;
+      element_geometry<DIM>(p, G);
+      const double meas = fabs(G.det);
+      if (A.form.pm | A.form.ps) {
+        double h = DIM == 2 ? sqrt(meas) : cbrt(meas);
+        cm *= ipow(h, A.form.pm); cs *= ipow(h, A.form.ps);
+      }
+      bary_gradients<DIM>(G, gl);
+      double scale = 1.0;
+      if (cut && IFACE) {                                              // |F^-T n_ref|
+        double g2 = 0.0, r2 = 0.0;
+#pragma unroll
+        for (int d = 0; d < DIM; d++) {
+          double v = 0.0;
+#pragma unroll
+          for (int k = 0; k <= DIM; k++) v += ls[k] * gl[k][d];
+          g2 += v * v;
+        }
+#pragma unroll
+        for (int k = 0; k < DIM; k++) { double v = ls[k] - ls[DIM]; r2 += v * v; }
+        scale = sqrt(g2) / sqrt(r2);
+      }
+      CutEntry E;
+      if (cut) E = lut[mask]; else { E.ns = 1; E.npt = 0; }
+      const double4 *rule = (cut && IFACE) ? srule_if : srule_vol;
+      const int nr = (cut && IFACE) ? A.nr_if : A.nr_vol;
+      for (int sub = 0; sub < E.ns; sub++) {
+        double P[4][3];
+        double sfac = 1.0;
+        if (cut) {
+#pragma unroll
+          for (int v = 0; v < NPT; v++) coded_point<DIM>(E.v[sub][v], ls, P[v]);
+          sfac = simplex_factor(NPT, P);
+        }
+        const double f0 = meas * sfac * scale;
+        for (int q = 0; q < nr; q++) {
+          const double4 r = rule[q];
+          double xi[3] = {r.x, r.y, r.z};
+          if (cut) simplex_point(NPT, P, r, xi);
+          double lam[NV], fl[NV];
+          double last = 1.0;
+#pragma unroll
+          for (int k = 0; k < DIM; k++) { lam[k] = xi[k]; last -= xi[k]; }
+          lam[DIM] = last;
+          const double f = f0 * r.w;
+          m0 += f;
+#pragma unroll
+          for (int a = 0; a < NV; a++) {
+            fl[a] = f * lam[a];
+#pragma unroll
+            for (int b = 0; b <= a; b++) m2[a * (a + 1) / 2 + b] = fma(fl[a], lam[b], m2[a * (a + 1) / 2 + b]);
+          }
+          if constexpr (ORDER == 2) {
+            double ep[NT];
+#pragma unroll
+            for (int ed = 0; ed < NEDGE; ed++) {
+              int a, b;
+              edge_vertices<DIM>(ed, a, b);
+              ep[ed] = lam[a] * lam[b];
+            }
+#pragma unroll
+            for (int a = 0; a < NV; a++) {
+              m1[a] += fl[a];
+#pragma unroll
+              for (int ed = 0; ed < NEDGE; ed++) mT[a][ed] = fma(fl[a], ep[ed], mT[a][ed]);
+            }
+            int t = 0;
+#pragma unroll
+            for (int ed = 0; ed < NEDGE; ed++) {
+              const double fe = f * ep[ed];
+#pragma unroll
+              for (int e2 = 0; e2 <= ed; e2++) { mQ[t] = fma(fe, ep[e2], mQ[t]); t++; }
+            }
+          }
+        }
+      }
+    }
+    // expand: gram matrix of the barycentric gradients, then the lower triangle (mirrored on store)
+    double gm[N2];
+#pragma unroll
+    for (int a = 0; a < NV; a++)
+#pragma unroll
+      for (int b = 0; b <= a; b++) {
+        double v = 0.0;
+#pragma unroll
+        for (int d = 0; d < DIM; d++) v = fma(gl[a][d], gl[b][d], v);
+        gm[a * (a + 1) / 2 + b] = cs * v;
+      }
+    double *out = A.elmats + s * NE;
+#pragma unroll
+    for (int i = 0; i < NV; i++)
+#pragma unroll
+      for (int j = 0; j <= i; j++) {
+        const double v = fma(cm, m2[sym2(i, j)], gm[sym2(i, j)] * m0);
+        out[i * ND + j] = v;
+        if (j != i) out[j * ND + i] = v;
+      }
+    if constexpr (ORDER == 2) {
+      int t = 0;
+#pragma unroll
+      for (int ed = 0; ed < NEDGE; ed++) {
+        int a, b;
+        edge_vertices<DIM>(ed, a, b);
+        const int i = NV + ed;
+#pragma unroll
+        for (int j = 0; j < NV; j++) {
+          const double st = fma(gm[sym2(j, a)], m1[b], gm[sym2(j, b)] * m1[a]);
+          const double v = -0.5 * fma(cm, mT[j][ed], st);
+          out[i * ND + j] = v;
+          out[j * ND + i] = v;
+        }
+#pragma unroll
+        for (int e2 = 0; e2 <= ed; e2++) {
+          int c, d;
+          edge_vertices<DIM>(e2, c, d);
+          double st = gm[sym2(a, c)] * m2[sym2(b, d)];
+          st = fma(gm[sym2(a, d)], m2[sym2(b, c)], st);
+          st = fma(gm[sym2(b, c)], m2[sym2(a, d)], st);
+          st = fma(gm[sym2(b, d)], m2[sym2(a, c)], st);
+          const double v = 0.25 * fma(cm, mQ[t], st);
+          t++;
+          out[i * ND + NV + e2] = v;
+          if (e2 != ed) out[(NV + e2) * ND + i] = v;
+        }
+      }
+    }
+  }
+}
+
+static int g_use_fast = 1;
+
 template <int DIM, int ORDER, bool IFACE>
 static int launch_cutmat_t(const ElmatArgs &A, int sm_count, int64_t maxcount, cudaStream_t st) {
   size_t smem = (size_t)(A.nr_vol + A.nr_if) * sizeof(double4) + 16 * sizeof(CutEntry);
-  auto kern = k_cutmat<DIM, ORDER, IFACE>;
+  const bool mom = g_use_fast && A.form.cn == 0.0 && A.form.cd == 0.0;
+  auto kern = mom ? k_cutmat_mom<DIM, ORDER, IFACE> : k_cutmat<DIM, ORDER, IFACE>;
   int occ = 0;
   NGSX_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, kern, CUTMAT_THREADS, smem));
   if (occ < 1) { set_error("cut-element kernel does not fit on an SM"); return NGSX_ERR_CUDA; }
@@ -839,7 +1021,6 @@ static int launch_cutmat(const ElmatArgs &A, int fe_order, int sm_count, int64_t
   return NGSX_ERR_UNSUPPORTED;
 }
 
-static int g_use_fast = 1;
 // optional per-kernel timing of the row-gather assembly (bench.py roofline): CUDA events on the launch stream
 static int g_timing = 0;
 static cudaEvent_t g_ev[4];
