@@ -7,6 +7,13 @@
 #include <mutex>
 #include <vector>
 #include "ngsx_host.cuh"
+#include "ngsx_stream.cuh"
+#ifndef NGSX_INT_MINB
+#define NGSX_INT_MINB 2      // resident CTAs per SM of the streamed sweeps (64 KB of stages each; 3 forces 80 registers and spills)
+#endif
+#ifndef NGSX_CLS_MINB
+#define NGSX_CLS_MINB 2
+#endif
 #include "rule_tables.h"
 
 namespace ngsx {
@@ -97,6 +104,13 @@ const DeviceData *device_data() {
       cudaDeviceGetAttribute(&dd.sm_count, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess) {
     set_error(std::string("device_data: ") + cudaGetErrorString(cudaGetLastError()));
     return nullptr;
+  }
+  // per-call scratch comes from the stream-ordered pool: keep up to 2 GB of it mapped across synchronisation points (the
+  // default threshold 0 unmaps everything at every cudaEventSynchronize and re-maps ~100 MB in the next Integrate)
+  cudaMemPool_t pool;
+  if (cudaDeviceGetDefaultMemPool(&pool, dev) == cudaSuccess) {
+    uint64_t keep = 1ull << 31;
+    cudaMemPoolSetAttribute(pool, cudaMemPoolAttrReleaseThreshold, &keep);
   }
   g_dd[dev] = dd;
   g_dd_ready[dev] = true;
@@ -189,9 +203,8 @@ __global__ void k_lset_cf(int dim, int64_t nv, const double *__restrict__ vert, 
 }
 
 // sum over the sub-simplices of (dt) of the measure factor: the order-0 part volume divided by the rule weight
-// (out of line: only the ~1.5 % cut elements need it, keeping it out of the hot path's register budget)
 template <int DIM>
-__device__ __noinline__ double part_factor(const CutEntry &E, const double *ls) {
+__device__ __forceinline__ double part_factor(const CutEntry &E, const double *ls) {
   double s = 0.0;
   for (int k = 0; k < E.ns; k++) {
     double P[4][3];
@@ -201,46 +214,129 @@ __device__ __noinline__ double part_factor(const CutEntry &E, const double *ls) 
   return s;
 }
 
-// (a) one thread per element; one warp = one 32-bit word of every bit array (ballot, no atomics)
-template <int DIM>
-__global__ void __launch_bounds__(256) k_classify(ngsx_mesh M, const double *__restrict__ lset, const CutTable *__restrict__ tab,
-                                                 uint32_t *__restrict__ words, int64_t nwords, int8_t *__restrict__ dom_out,
-                                                 double *__restrict__ ratio, unsigned long long *__restrict__ err) {
-  int64_t e = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-  int dom = -2;                                        // -2: beyond ne
-  if (e < M.ne) {
-    int v[4], mask;
-    double ls[4];
-    load_element<DIM>(M, lset, e, v, ls, (double(*)[DIM]) nullptr);
-    dom = sign_test<DIM>(ls, mask);
-    if (ratio) {
-      double r = dom == NEG ? 1.0 : 0.0;
-      if (dom == IF) {                                 // xfem/cutinfo.cpp:79-91 (the common rule weight cancels)
-        double vn = part_factor<DIM>(tab->e[DIM - 2][NEG][mask], ls), vp = part_factor<DIM>(tab->e[DIM - 2][POS][mask], ls);
-        r = vn / (vn + vp);
-      }
-      if (dom == -1) r = nan("");
-      ratio[e] = r;
-    }
-    if (dom_out) dom_out[e] = (int8_t)dom;
-    if (dom == -1 && err) {
-      atomicAdd(&err[0], 1ULL);
-      atomicMin(reinterpret_cast<long long *>(&err[1]), (long long)e);
+// (a) classification, two passes:
+//   k_classify: persistent CTAs stream the element table (ngsx_stream.cuh); a warp owns four words of every bit array per chunk
+//   (ballot, no atomics), issues the 16 level-set gathers of its four elements together, writes domains, the eight bit
+//   arrays and the cut ratio of the uncut elements (1 / 0).
+//   k_classify_cut: the cut ratio of the IF elements (xfem/cutinfo.cpp:79-91: NEG part / (NEG + POS part); the common rule
+//   weight cancels), densely packed from the IF bit array -- fused into the first pass, the sub-simplex walk ran with one or
+//   two live lanes in 3 of 4 warps (4 % cut elements: 73 % of the warps hold one) and made the sweep instruction bound.
+template <int DIM, bool FULL>
+__device__ __forceinline__ void classify_chunk(const ngsx_mesh &M, const double *__restrict__ lset, uint32_t *__restrict__ words,
+                                               uint32_t *__restrict__ ifwords, int64_t nwords, int8_t *__restrict__ dom_out,
+                                               double *__restrict__ ratio, unsigned long long *__restrict__ err, int64_t c, int64_t first, int n,
+                                               const int32_t *stage, int nstaged) {
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  int v[STREAM_WPW][4];
+  double ls[STREAM_WPW][4];
+#pragma unroll
+  for (int k = 0; k < STREAM_WPW; k++) {
+    const int i = (warp * STREAM_WPW + k) * 32 + lane;
+    if (FULL || i < n) stream_vertices<DIM>(stage, FULL ? STREAM_CH : nstaged, M.el2v, first, i, v[k]);
+  }
+#pragma unroll
+  for (int k = 0; k < STREAM_WPW; k++) {
+    const int i = (warp * STREAM_WPW + k) * 32 + lane;
+    if (FULL || i < n) {
+#pragma unroll
+      for (int a = 0; a <= DIM; a++) ls[k][a] = __ldg(lset + v[k][a]);
     }
   }
-  if (words) {
-    unsigned bn = __ballot_sync(0xffffffffu, dom == NEG), bp = __ballot_sync(0xffffffffu, dom == POS);
-    unsigned bi = __ballot_sync(0xffffffffu, dom == IF), ba = __ballot_sync(0xffffffffu, dom != -2);
-    int64_t w = e >> 5;
-    if ((threadIdx.x & 31) == 0 && w < nwords) {
-      words[NGSX_CDOM_NO * nwords + w] = 0u;
-      words[NGSX_CDOM_NEG * nwords + w] = bn;
-      words[NGSX_CDOM_POS * nwords + w] = bp;
-      words[NGSX_CDOM_UNCUT * nwords + w] = bn | bp;
-      words[NGSX_CDOM_IF * nwords + w] = bi;
-      words[NGSX_CDOM_HASNEG * nwords + w] = bn | bi;
-      words[NGSX_CDOM_HASPOS * nwords + w] = bp | bi;
-      words[NGSX_CDOM_ANY * nwords + w] = ba;
+  unsigned bn[STREAM_WPW], bp[STREAM_WPW], bi[STREAM_WPW], ba[STREAM_WPW];
+#pragma unroll
+  for (int k = 0; k < STREAM_WPW; k++) {
+    const int i = (warp * STREAM_WPW + k) * 32 + lane;
+    const int64_t e = first + i;
+    int dom = -2;                                    // -2: beyond ne
+    if (FULL || i < n) {
+      int mask;
+      dom = sign_test<DIM>(ls[k], mask);
+      if (ratio && dom != IF) ratio[e] = dom == NEG ? 1.0 : (dom == POS ? 0.0 : nan(""));
+      if (dom_out) dom_out[e] = (int8_t)dom;
+      if (dom == -1 && err) {
+        atomicAdd(&err[0], 1ULL);
+        atomicMin(reinterpret_cast<long long *>(&err[1]), (long long)e);
+      }
+    }
+    bn[k] = __ballot_sync(0xffffffffu, dom == NEG); bp[k] = __ballot_sync(0xffffffffu, dom == POS);
+    bi[k] = __ballot_sync(0xffffffffu, dom == IF); ba[k] = __ballot_sync(0xffffffffu, dom != -2);
+  }
+  // the warp's 4 words of the 8 bit arrays in one store: lane = array * 4 + word.  The array number is the bit pattern
+  // {NEG, POS, IF} of the domains it collects (NGSX_CDOM_*), except ANY = every element
+  const int kk = lane & 3, arr = lane >> 2;
+  const unsigned n_ = kk == 0 ? bn[0] : kk == 1 ? bn[1] : kk == 2 ? bn[2] : bn[3];
+  const unsigned p_ = kk == 0 ? bp[0] : kk == 1 ? bp[1] : kk == 2 ? bp[2] : bp[3];
+  const unsigned i_ = kk == 0 ? bi[0] : kk == 1 ? bi[1] : kk == 2 ? bi[2] : bi[3];
+  const unsigned a_ = kk == 0 ? ba[0] : kk == 1 ? ba[1] : kk == 2 ? ba[2] : ba[3];
+  const unsigned sel = arr == NGSX_CDOM_ANY ? a_ : (((arr & 1) ? n_ : 0u) | ((arr & 2) ? p_ : 0u) | ((arr & 4) ? i_ : 0u));
+  const int64_t w = c * (STREAM_CH / 32) + warp * STREAM_WPW + kk;
+  if (w < nwords) {
+    if (words) words[arr * nwords + w] = sel;
+    if (ifwords && arr == NGSX_CDOM_IF) ifwords[w] = sel;
+  }
+}
+
+template <int DIM>
+__global__ void __launch_bounds__(STREAM_THREADS, NGSX_CLS_MINB) k_classify(ngsx_mesh M, const double *__restrict__ lset, uint32_t *__restrict__ words,
+                                                               uint32_t *__restrict__ ifwords, int64_t nwords, int8_t *__restrict__ dom_out,
+                                                               double *__restrict__ ratio, unsigned long long *__restrict__ err) {
+  extern __shared__ __align__(128) unsigned char smem_stream[];
+  stream_elements<DIM>(M, smem_stream, [&](int64_t c, int64_t first, int n, const int32_t *stage, int nstaged) {
+    if (n == STREAM_CH) classify_chunk<DIM, true>(M, lset, words, ifwords, nwords, dom_out, ratio, err, c, first, n, stage, nstaged);
+    else classify_chunk<DIM, false>(M, lset, words, ifwords, nwords, dom_out, ratio, err, c, first, n, stage, nstaged);
+  });
+}
+
+constexpr int CUT_G = 4;     // chunks of 32 mask words per CTA of the cut passes
+
+// volume parts only (DIM + 1 points per sub-simplex): unrolled, the points stay in registers
+template <int DIM>
+__device__ __forceinline__ double part_volume(const CutEntry &E, const double *ls) {
+  double s = 0.0;
+  const int ns = E.ns;
+  for (int k = 0; k < ns; k++) {
+    double P[4][3];
+#pragma unroll
+    for (int v = 0; v <= DIM; v++) coded_point<DIM>(E.v[k][v], ls, P[v]);
+    s += simplex_factor(DIM + 1, P);
+  }
+  return s;
+}
+
+// one CTA per CUT_G chunks of 32 IF words (1024 elements each; most chunks hold no cut element); every warp scans the
+// chunks, warp w takes the rounds (w - g) mod 8, + 8, ... of 32 items of chunk g; item = (cut element, NEG / POS part) on a lane pair, so
+// the two part volumes of an element run side by side.  (Chunks per persistent warp left a 7x imbalance between SMs: the cut
+// elements of a sphere cluster where the surface is tangential to the element numbering.)
+template <int DIM>
+__global__ void __launch_bounds__(256) k_classify_cut(ngsx_mesh M, const double *__restrict__ lset, const CutTable *__restrict__ tab,
+                                                     const uint32_t *__restrict__ ifwords, int64_t nwords, double *__restrict__ ratio) {
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  uint32_t cwg[CUT_G];
+#pragma unroll
+  for (int g = 0; g < CUT_G; g++) {
+    const int64_t w = ((int64_t)blockIdx.x * CUT_G + g) * 32 + lane;
+    cwg[g] = w < nwords ? __ldg(ifwords + w) : 0u;
+  }
+#pragma unroll
+  for (int g = 0; g < CUT_G; g++) {
+    const int64_t c = (int64_t)blockIdx.x * CUT_G + g;
+    BitDeal D;
+    D.scan(cwg[g], lane);
+    for (int r0 = 32 * ((warp - g) & 7); r0 < 2 * D.total; r0 += 32 * 8) {
+      int owner;
+      const int bit = D.item((r0 + lane) >> 1, owner);
+      double vol = 0.0;
+      int64_t e = 0;
+      if (bit >= 0) {
+        e = ((c * 32 + owner) << 5) + bit;
+        int v[4], mask;
+        double ls[4];
+        load_element<DIM>(M, lset, e, v, ls, (double(*)[DIM]) nullptr);
+        sign_test<DIM>(ls, mask);
+        vol = part_volume<DIM>(tab->e[DIM - 2][lane & 1][mask], ls);          // even lane: NEG (0), odd lane: POS (1)
+      }
+      const double other = __shfl_xor_sync(0xffffffffu, vol, 1);
+      if (bit >= 0 && !(lane & 1)) ratio[e] = vol / (vol + other);
     }
   }
 }
@@ -386,85 +482,124 @@ __device__ __forceinline__ void map_point(const double (*p)[DIM], const double *
 //      the seven others of its block: measured 0.32 ms with a block tree against 0.24 ms without).
 //   2. k_reduce_final: fixed-shape tree over the warp partials.
 // Every partial sum has a shape that depends on ne only: bitwise reproducible, no floating-point atomics.
-// phase 1 (lean: full occupancy): sign test, cut mask of the warp, integral of the uncut elements of the domain
-template <int DIM>
-__global__ void __launch_bounds__(256) k_int_uncut(ngsx_mesh M, const double *__restrict__ lset, int dt, const double4 *__restrict__ rule_vol, int nr_vol,
-                                                  PolyDev f, int fconst, double wref_vol, double *__restrict__ partial, uint32_t *__restrict__ cutwords) {
-  const int64_t e = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-  int v[4] = {0, 0, 0, 0}, mask = 0;
-  double ls[4];
-  int dom = -1;
-  if (e < M.ne) {
-    load_element<DIM>(M, lset, e, v, ls, (double(*)[DIM]) nullptr);
-    dom = sign_test<DIM>(ls, mask);
+// phase 1 (lean): sign test, cut mask of every word, integral of the uncut elements of the domain.  Persistent CTAs stream the
+// element table (ngsx_stream.cuh); a warp owns four words per chunk and issues the gathers of its four elements together.
+template <int DIM, bool FULL>
+__device__ __forceinline__ void int_uncut_chunk(const ngsx_mesh &M, const double *__restrict__ lset, int dt, const double4 *__restrict__ rule_vol,
+                                                int nr_vol, const PolyDev &f, int fconst, double wref_vol, double *__restrict__ partial,
+                                                uint32_t *__restrict__ cutwords, int64_t nred, int64_t c, int64_t first, int n,
+                                                const int32_t *stage, int nstaged) {
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  int v[STREAM_WPW][4];
+  double ls[STREAM_WPW][4];
+#pragma unroll
+  for (int k = 0; k < STREAM_WPW; k++) {
+    const int i = (warp * STREAM_WPW + k) * 32 + lane;
+    if (FULL || i < n) stream_vertices<DIM>(stage, FULL ? STREAM_CH : nstaged, M.el2v, first, i, v[k]);
   }
-  const uint32_t cw = __ballot_sync(0xffffffffu, dom == IF);
-  double val = 0.0;
-  if (dom == dt && dt != IF) {
-    double p[DIM + 1][DIM];
 #pragma unroll
-    for (int k = 0; k <= DIM; k++)
+  for (int k = 0; k < STREAM_WPW; k++) {
+    const int i = (warp * STREAM_WPW + k) * 32 + lane;
+    if (FULL || i < n) {
 #pragma unroll
-      for (int d = 0; d < DIM; d++) p[k][d] = __ldg(M.vert + (int64_t)v[k] * DIM + d);
-    ElGeom<DIM> G;
-    element_geometry<DIM>(p, G);
-    const double meas = fabs(G.det);
-    if (fconst) {
-      val = meas * (wref_vol * f.c[0]);
-    } else {
-      for (int q = 0; q < nr_vol; q++) {
-        const double4 r = rule_vol[q];
-        double xi[3] = {r.x, r.y, r.z}, x[3];
-        map_point<DIM>(p, xi, x);
-        val += meas * r.w * eval_poly(f, x);
+      for (int a = 0; a <= DIM; a++) ls[k][a] = __ldg(lset + v[k][a]);
+    }
+  }
+  double val[STREAM_WPW];
+  uint32_t cw[STREAM_WPW];
+#pragma unroll
+  for (int k = 0; k < STREAM_WPW; k++) {
+    const int i = (warp * STREAM_WPW + k) * 32 + lane;
+    int dom = -1, mask;
+    if (FULL || i < n) dom = sign_test<DIM>(ls[k], mask);
+    cw[k] = __ballot_sync(0xffffffffu, dom == IF);
+    val[k] = 0.0;
+    if (dom == dt && dt != IF) {
+      double p[DIM + 1][DIM];
+#pragma unroll
+      for (int a = 0; a <= DIM; a++)
+#pragma unroll
+        for (int d = 0; d < DIM; d++) p[a][d] = __ldg(M.vert + (int64_t)v[k][a] * DIM + d);
+      ElGeom<DIM> G;
+      element_geometry<DIM>(p, G);
+      const double meas = fabs(G.det);
+      if (fconst) {
+        val[k] = meas * (wref_vol * f.c[0]);
+      } else {
+        double sum = 0.0;
+        for (int q = 0; q < nr_vol; q++) {
+          const double4 r = rule_vol[q];
+          double xi[3] = {r.x, r.y, r.z}, x[3];
+          map_point<DIM>(p, xi, x);
+          sum += meas * r.w * eval_poly(f, x);
+        }
+        val[k] = sum;
       }
     }
   }
 #pragma unroll
-  for (int o = 16; o > 0; o >>= 1) val += __shfl_xor_sync(0xffffffffu, val, o);
-  if ((threadIdx.x & 31) == 0) { partial[e >> 5] = val; cutwords[e >> 5] = cw; }
+  for (int k = 0; k < STREAM_WPW; k++) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) val[k] += __shfl_xor_sync(0xffffffffu, val[k], o);
+  }
+  if (lane < STREAM_WPW) {
+    const int64_t w = c * (STREAM_CH / 32) + warp * STREAM_WPW + lane;
+    if (w < nred) {
+      partial[w] = lane == 0 ? val[0] : lane == 1 ? val[1] : lane == 2 ? val[2] : val[3];
+      cutwords[w] = lane == 0 ? cw[0] : lane == 1 ? cw[1] : lane == 2 ? cw[2] : cw[3];
+    }
+  }
 }
 
-// phase 2: the cut elements (1.5 % at config 2), densely packed.  Persistent warps walk chunks of 32 mask words (1024
-// elements); the set bits of a chunk are enumerated in (word, bit) order and dealt out 32 at a time, one cut element per
-// lane, so every lane of a round works.  The values of one word are then summed in bit order by a segmented shuffle loop
-// and handed to the lane that owns the word; each word's partial gets uncut sum + cut sum from a single writer.
-// Fixed order everywhere: bitwise reproducible, no atomics.
 template <int DIM>
-__global__ void __launch_bounds__(256) k_int_cut(ngsx_mesh M, const double *__restrict__ lset, const CutTable *__restrict__ tab, int dt,
+__global__ void __launch_bounds__(STREAM_THREADS, NGSX_INT_MINB) k_int_uncut(ngsx_mesh M, const double *__restrict__ lset, int dt, const double4 *__restrict__ rule_vol,
+                                                                int nr_vol, PolyDev f, int fconst, double wref_vol, double *__restrict__ partial,
+                                                                uint32_t *__restrict__ cutwords, int64_t nred) {
+  extern __shared__ __align__(128) unsigned char smem_stream[];
+  stream_elements<DIM>(M, smem_stream, [&](int64_t c, int64_t first, int n, const int32_t *stage, int nstaged) {
+    if (n == STREAM_CH) int_uncut_chunk<DIM, true>(M, lset, dt, rule_vol, nr_vol, f, fconst, wref_vol, partial, cutwords, nred, c, first, n, stage, nstaged);
+    else int_uncut_chunk<DIM, false>(M, lset, dt, rule_vol, nr_vol, f, fconst, wref_vol, partial, cutwords, nred, c, first, n, stage, nstaged);
+  });
+  // words beyond the last chunk (the reduction length is padded to a multiple of 8 words)
+  const int64_t wend = ((M.ne + STREAM_CH - 1) / STREAM_CH) * (STREAM_CH / 32);
+  if (blockIdx.x == 0)
+    for (int64_t w = wend + threadIdx.x; w < nred; w += blockDim.x) { partial[w] = 0.0; cutwords[w] = 0u; }
+}
+
+// phase 2: the cut elements (1.5 % at config 2), densely packed.  One CTA per CUT_G chunks of 32 mask words (1024 elements
+// each; most chunks hold no cut element -- persistent warps with whole chunks each left a 7x imbalance between
+// SMs, the cut elements of a sphere cluster where the surface is tangential to the element numbering).  Every warp scans the
+// chunks; the set bits are enumerated in (word, bit) order and dealt out 32 at a time, one cut element per lane, warp w taking
+// rounds (w - g) mod 8, + 8, ... of chunk g.  The values of one word are summed in bit order by a segmented shuffle loop and handed to the lane that
+// owns the word; the per-warp word sums are combined in warp order and added to the word's partial by a single writer.
+// Fixed order everywhere: bitwise reproducible, no atomics.
+template <int DIM, bool IFACE, bool FCONST>
+__global__ void __launch_bounds__(256, FCONST ? 3 : 2) k_int_cut(ngsx_mesh M, const double *__restrict__ lset, const CutTable *__restrict__ tab, int dt,
                                                 const double4 *__restrict__ rule_vol, int nr_vol, const double4 *__restrict__ rule_if, int nr_if,
                                                 PolyDev f, int fconst, double wref_vol, double wref_if, const uint32_t *__restrict__ cutwords,
                                                 int64_t nwords, double *__restrict__ partial) {
-  const int lane = threadIdx.x & 31;
-  const int64_t nchunks = (nwords + 31) >> 5;
-  const int64_t nwarps = (int64_t)gridDim.x * (blockDim.x >> 5);
-  for (int64_t c = (int64_t)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5); c < nchunks; c += nwarps) {
-    const int64_t w = c * 32 + lane;
-    const uint32_t cw = w < nwords ? __ldg(cutwords + w) : 0u;
-    const int cnt = __popc(cw);
-    int end = cnt;                                   // inclusive prefix sum of the bit counts
+  __shared__ double accs[CUT_G][8][32];
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  uint32_t cwg[CUT_G];
+  uint32_t mine = 0u;                                // warp g < CUT_G finishes chunk g
 #pragma unroll
-    for (int o = 1; o < 32; o <<= 1) { const int t = __shfl_up_sync(0xffffffffu, end, o); if (lane >= o) end += t; }
-    const int total = __shfl_sync(0xffffffffu, end, 31);
-    if (total == 0) continue;
-    const int begin = end - cnt;
-    double acc = 0.0;                                // cut sum of this lane's word
-    for (int r0 = 0; r0 < total; r0 += 32) {
-      const int t = r0 + lane;
-      // owner = number of words whose items all precede item t (binary search over the prefix sums)
-      int owner = 0;
+  for (int g = 0; g < CUT_G; g++) {
+    const int64_t w = ((int64_t)blockIdx.x * CUT_G + g) * 32 + lane;
+    cwg[g] = w < nwords ? __ldg(cutwords + w) : 0u;
+    if (g == warp) mine = cwg[g];
+  }
 #pragma unroll
-      for (int step = 16; step > 0; step >>= 1) {
-        const int probe = owner + step - 1;
-        const int pe = __shfl_sync(0xffffffffu, end, probe & 31);
-        if (probe < 32 && pe <= t) owner += step;
-      }
-      owner = min(owner, 31);
-      const uint32_t ow = __shfl_sync(0xffffffffu, cw, owner);
-      const int ob = __shfl_sync(0xffffffffu, begin, owner);
+  for (int g = 0; g < CUT_G; g++) {
+    const int64_t c = (int64_t)blockIdx.x * CUT_G + g;
+    BitDeal D;
+    D.scan(cwg[g], lane);
+    const int total = D.total, begin = D.begin, end = D.end, cnt = D.cnt;
+    double acc = 0.0;                                // this warp's share of the cut sum of this lane's word
+    for (int r0 = 32 * ((warp - g) & 7); r0 < total; r0 += 32 * 8) {
+      int owner;
+      const int bit = D.item(r0 + lane, owner);
       double val = 0.0;
-      if (t < total) {
-        const int bit = (int)__fns(ow, 0u, t - ob + 1);
+      if (bit >= 0) {
         const int64_t e = ((c * 32 + owner) << 5) + bit;
         int v[4], mask;
         double ls[4], p[DIM + 1][DIM];
@@ -473,21 +608,24 @@ __global__ void __launch_bounds__(256) k_int_cut(ngsx_mesh M, const double *__re
         ElGeom<DIM> G;
         element_geometry<DIM>(p, G);
         const double meas = fabs(G.det);
-        const CutEntry E = tab->e[DIM - 2][dt][mask];
-        const double4 *rule = dt == IF ? rule_if : rule_vol;
-        const int nr = dt == IF ? nr_if : nr_vol;
-        const double scale = dt == IF ? interface_scale<DIM>(G, ls) : 1.0;
-        for (int sidx = 0; sidx < E.ns; sidx++) {
+        constexpr int NPT = IFACE ? DIM : DIM + 1;     // points of a sub-simplex: compile time, so they stay in registers
+        const CutEntry &E = tab->e[DIM - 2][dt][mask];
+        const double4 *rule = IFACE ? rule_if : rule_vol;
+        const int nr = IFACE ? nr_if : nr_vol;
+        const double scale = IFACE ? interface_scale<DIM>(G, ls) : 1.0;
+        const int ns = E.ns;
+        for (int sidx = 0; sidx < ns; sidx++) {
           double P[4][3];
-          for (int k = 0; k < E.npt; k++) coded_point<DIM>(E.v[sidx][k], ls, P[k]);
-          const double fac = simplex_factor(E.npt, P) * scale;
-          if (fconst) {
-            val += meas * (((dt == IF ? wref_if : wref_vol) * fac) * f.c[0]);
+#pragma unroll
+          for (int k = 0; k < NPT; k++) coded_point<DIM>(E.v[sidx][k], ls, P[k]);
+          const double fac = simplex_factor(NPT, P) * scale;
+          if constexpr (FCONST) {
+            val += meas * (((IFACE ? wref_if : wref_vol) * fac) * f.c[0]);
           } else {
             for (int q = 0; q < nr; q++) {
               double xi[3], x[3];
               const double4 rr = rule[q];
-              simplex_point(E.npt, P, rr, xi);
+              simplex_point(NPT, P, rr, xi);
               map_point<DIM>(p, xi, x);
               val += meas * (rr.w * fac) * eval_poly(f, x);
             }
@@ -506,12 +644,25 @@ __global__ void __launch_bounds__(256) k_int_cut(ngsx_mesh M, const double *__re
         if (!__any_sync(0xffffffffu, same)) break;
       }
       // word `lane` has items [begin, end) of the chunk; those of this round start at lane max(begin, r0) - r0
-      const int first = max(begin, r0) - r0;
-      const double got = __shfl_sync(0xffffffffu, seg, first & 31);
+      const int firstl = max(begin, r0) - r0;
+      const double got = __shfl_sync(0xffffffffu, seg, firstl & 31);
       if (cnt > 0 && begin < r0 + 32 && end > r0) acc += got;
     }
-    if (cnt > 0) partial[w] += acc;
+    accs[g][warp][lane] = acc;
   }
+  __syncthreads();
+  if (warp < CUT_G && mine != 0u) {
+    double sum = 0.0;
+#pragma unroll
+    for (int k = 0; k < 8; k++) sum += accs[warp][k][lane];
+    partial[((int64_t)blockIdx.x * CUT_G + warp) * 32 + lane] += sum;
+  }
+}
+
+template <int DIM, typename... Args>
+static void launch_int_cut(bool iface, bool fc, unsigned grid, cudaStream_t st, Args... a) {
+  if (iface) { if (fc) k_int_cut<DIM, true, true><<<grid, 256, 0, st>>>(a...); else k_int_cut<DIM, true, false><<<grid, 256, 0, st>>>(a...); }
+  else { if (fc) k_int_cut<DIM, false, true><<<grid, 256, 0, st>>>(a...); else k_int_cut<DIM, false, false><<<grid, 256, 0, st>>>(a...); }
 }
 
 // middle level: fixed grid, block-stride over the warp partials, fixed block tree -> one partial per block
@@ -636,9 +787,32 @@ int ngsx_classify(const ngsx_mesh *mesh, const double *lset_v, uint32_t *cdom_wo
   if (mesh->ne == 0) return NGSX_OK;
   int64_t nwords = (mesh->ne + 31) / 32;
   auto *e = reinterpret_cast<unsigned long long *>(err);
-  if (mesh->dim == 2) k_classify<2><<<nblocks(mesh->ne, 256), 256, 0, st>>>(*mesh, lset_v, dd->cut_table, cdom_words, nwords, dom, ratio, e);
-  else k_classify<3><<<nblocks(mesh->ne, 256), 256, 0, st>>>(*mesh, lset_v, dd->cut_table, cdom_words, nwords, dom, ratio, e);
-  NGSX_LAUNCH_CHECK();
+  NGSX_REQUIRE((reinterpret_cast<uintptr_t>(mesh->el2v) & 15u) == 0, "classify: mesh.el2v must be 16-byte aligned");
+  uint32_t *ifwords = cdom_words ? cdom_words + NGSX_CDOM_IF * nwords : nullptr, *tmp = nullptr;
+  if (ratio && !ifwords) {
+    NGSX_CUDA(cudaMallocAsync(&tmp, nwords * sizeof(uint32_t), st));
+    ifwords = tmp;
+  }
+  const int64_t nchunks = (mesh->ne + STREAM_CH - 1) / STREAM_CH;
+  const unsigned grid = (unsigned)std::min<int64_t>(nchunks, (int64_t)dd->sm_count * NGSX_CLS_MINB);
+  const unsigned gcut = (unsigned)(((nwords + 31) / 32 + CUT_G - 1) / CUT_G);      // one CTA per CUT_G chunks of 32 words
+  cudaError_t e0 = cudaSuccess;
+  if (mesh->dim == 2) {
+    static const cudaError_t attr = cudaFuncSetAttribute(k_classify<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)stream_smem<2>());
+    e0 = attr;
+    k_classify<2><<<grid, STREAM_THREADS, stream_smem<2>(), st>>>(*mesh, lset_v, cdom_words, tmp, nwords, dom, ratio, e);
+    if (ratio) k_classify_cut<2><<<gcut, 256, 0, st>>>(*mesh, lset_v, dd->cut_table, ifwords, nwords, ratio);
+  } else {
+    static const cudaError_t attr = cudaFuncSetAttribute(k_classify<3>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)stream_smem<3>());
+    e0 = attr;
+    k_classify<3><<<grid, STREAM_THREADS, stream_smem<3>(), st>>>(*mesh, lset_v, cdom_words, tmp, nwords, dom, ratio, e);
+    if (ratio) k_classify_cut<3><<<gcut, 256, 0, st>>>(*mesh, lset_v, dd->cut_table, ifwords, nwords, ratio);
+  }
+  cudaError_t e1 = cudaGetLastError();
+  g_launches.fetch_add(ratio ? 2 : 1);
+  if (tmp) cudaFreeAsync(tmp, st);
+  NGSX_CUDA(e0);
+  NGSX_CUDA(e1);
   return NGSX_OK;
 }
 
@@ -741,14 +915,21 @@ int ngsx_integrate(const ngsx_mesh *mesh, const double *lset_v, int dt, int orde
   uint32_t *cutwords = nullptr;
   NGSX_CUDA(cudaMallocAsync(&partial, (nred + nmid) * sizeof(double), st));
   NGSX_CUDA(cudaMallocAsync(&cutwords, nred * sizeof(uint32_t), st));
-  const unsigned nb = nblocks(ne, 256);
-  const unsigned ncut = (unsigned)std::max<int64_t>(1, std::min<int64_t>((nred + 255) / 256, (int64_t)dd->sm_count * 2));   // persistent
+  NGSX_REQUIRE((reinterpret_cast<uintptr_t>(mesh->el2v) & 15u) == 0, "integrate: mesh.el2v must be 16-byte aligned");
+  const int64_t nchunks = (ne + STREAM_CH - 1) / STREAM_CH;
+  const unsigned nb = (unsigned)std::min<int64_t>(nchunks, (int64_t)dd->sm_count * NGSX_INT_MINB);   // persistent
+  const unsigned ncut = (unsigned)(((nred + 31) / 32 + CUT_G - 1) / CUT_G);                    // one CTA per CUT_G chunks of 32 words
+  cudaError_t e0;
   if (mesh->dim == 2) {
-    k_int_uncut<2><<<nb, 256, 0, st>>>(*mesh, lset_v, dt, rv, nv, f, fconst, wref_vol, partial, cutwords);
-    k_int_cut<2><<<ncut, 256, 0, st>>>(*mesh, lset_v, dd->cut_table, dt, rv, nv, ri, ni, f, fconst, wref_vol, wref_if, cutwords, nred, partial);
+    static const cudaError_t attr = cudaFuncSetAttribute(k_int_uncut<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)stream_smem<2>());
+    e0 = attr;
+    k_int_uncut<2><<<nb, STREAM_THREADS, stream_smem<2>(), st>>>(*mesh, lset_v, dt, rv, nv, f, fconst, wref_vol, partial, cutwords, nred);
+    launch_int_cut<2>(dt == IF, fconst, ncut, st, *mesh, lset_v, dd->cut_table, dt, rv, nv, ri, ni, f, fconst, wref_vol, wref_if, cutwords, nred, partial);
   } else {
-    k_int_uncut<3><<<nb, 256, 0, st>>>(*mesh, lset_v, dt, rv, nv, f, fconst, wref_vol, partial, cutwords);
-    k_int_cut<3><<<ncut, 256, 0, st>>>(*mesh, lset_v, dd->cut_table, dt, rv, nv, ri, ni, f, fconst, wref_vol, wref_if, cutwords, nred, partial);
+    static const cudaError_t attr = cudaFuncSetAttribute(k_int_uncut<3>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)stream_smem<3>());
+    e0 = attr;
+    k_int_uncut<3><<<nb, STREAM_THREADS, stream_smem<3>(), st>>>(*mesh, lset_v, dt, rv, nv, f, fconst, wref_vol, partial, cutwords, nred);
+    launch_int_cut<3>(dt == IF, fconst, ncut, st, *mesh, lset_v, dd->cut_table, dt, rv, nv, ri, ni, f, fconst, wref_vol, wref_if, cutwords, nred, partial);
   }
   cudaError_t e1 = cudaGetLastError();
   k_int_reduce<<<nmid, 256, 0, st>>>(nred, partial, partial + nred);
@@ -756,6 +937,7 @@ int ngsx_integrate(const ngsx_mesh *mesh, const double *lset_v, int dt, int orde
   g_launches.fetch_add(4);
   cudaError_t e2 = cudaGetLastError();
   cudaFreeAsync(partial, st); cudaFreeAsync(cutwords, st);
+  NGSX_CUDA(e0);
   NGSX_CUDA(e1);
   NGSX_CUDA(e2);
   return NGSX_OK;

@@ -7,7 +7,9 @@ frac = float(sys.argv[3]) if len(sys.argv) > 3 else 0.008
 out = subprocess.run(['ncu', '-i', rep, '--page', 'source', '--csv', '--kernel-name', 'regex:' + kern], capture_output=True, text=True).stdout
 rows = list(csv.reader(out.splitlines()))
 start = next(i for i, r in enumerate(rows) if r and r[0] == 'Address')
-hdr, data = rows[start], [r for r in rows[start + 1:] if len(r) > 10]
+hdr = rows[start]
+end = next((i for i in range(start + 1, len(rows)) if rows[i] and rows[i][0] == 'Address'), len(rows))   # first matching launch only
+data = [r for r in rows[start + 1:end] if len(r) > 10]
 col = {n: hdr.index(n) for n in ('# Samples', 'Instructions Executed', 'Source', 'stall_long_sb', 'stall_short_sb', 'stall_mio', 'stall_wait',
                                   'stall_lg', 'Avg. Threads Executed', 'stall_math', 'stall_barrier', 'stall_not_selected', 'stall_branch_resolving')}
 S = lambda r, n: int(r[col[n]] or 0)
