@@ -112,7 +112,8 @@ def build_problem(nx, device, rank=0, world=1, group=6):
         # rows (halo elements are evaluated twice, nothing is exchanged)
         from ngsxfem_b200 import partition
         from ngsxfem_b200.ngs import BitArray
-        owner = partition.row_owners(Vh.el2dof[active], Vh.ndof, world)
+        cost = 1.0 + 2.2 * (ci.dom[active.long()] == xfem.IF).to(torch.float64)      # cut element: quadrature block + gather ~ 3.2x an uncut one
+        owner = partition.row_owners(Vh.el2dof[active], Vh.ndof, world, weights=cost)
         row_owner = (owner, rank)
         mine_els = partition.elements_of_owner(Vh.el2dof, active, owner, rank)
         mine = torch.zeros(mesh.ne, dtype=torch.bool, device=device)
@@ -163,16 +164,36 @@ def run_b200(args):
     ev = lambda: torch.cuda.Event(enable_timing=True)
     stage_ms = {"classify": [], "assemble": [], "integrate": []}
 
+    # classification, assembly and the two Integrate() calls depend on the level set only: issued on four streams, the
+    # latency-bound sweeps and cut passes overlap the assembly chain (N = 1: 1.33 -> 1.22 ms).  At N > 1 every kernel is short
+    # and the extra stream bookkeeping on the host costs more than the overlap gains (measured at N = 4: 0.50 ms serial,
+    # 0.57 ms on four streams), so the ranks of a multi-GPU run keep one stream.
+    main = torch.cuda.current_stream()
+    side = [torch.cuda.Stream() for _ in range(3)]
+    serial = world > 1 or bool(os.environ.get("NGSX_BENCH_SERIAL"))      # NGSX_BENCH_SERIAL: A/B switch at N = 1
+
     def step(record):
-        e = [ev() for _ in range(4)]
+        e = [ev() for _ in range(6)]
         e[0].record()
-        ci.Update(lsetp1)
-        e[1].record()
-        a.Assemble()
-        e[2].record()
-        s_if = xfem.IntegrateX(lsetp1, mesh_int, cf=1.0, order=4, domain_type=xfem.IF, sync=False)
-        s_neg = xfem.IntegrateX(lsetp1, mesh_int, cf=1.0, order=4, domain_type=xfem.NEG, sync=False)
-        e[3].record()
+        if serial:
+            ci.Update(lsetp1); e[1].record()
+            a.Assemble(); e[2].record()
+            s_if = xfem.IntegrateX(lsetp1, mesh_int, cf=1.0, order=4, domain_type=xfem.IF, sync=False); e[3].record()
+            s_neg = xfem.IntegrateX(lsetp1, mesh_int, cf=1.0, order=4, domain_type=xfem.NEG, sync=False); e[4].record()
+        else:
+            a.Assemble(); e[2].record()                                  # the longest chain first, on the main stream
+            for st in side:
+                st.wait_event(e[0])
+            with torch.cuda.stream(side[0]):
+                ci.Update(lsetp1); e[1].record()
+            with torch.cuda.stream(side[1]):
+                s_if = xfem.IntegrateX(lsetp1, mesh_int, cf=1.0, order=4, domain_type=xfem.IF, sync=False); e[3].record()
+            with torch.cuda.stream(side[2]):
+                s_neg = xfem.IntegrateX(lsetp1, mesh_int, cf=1.0, order=4, domain_type=xfem.NEG, sync=False); e[4].record()
+            for st in side:
+                main.wait_stream(st)
+            s_if.record_stream(main); s_neg.record_stream(main)
+        e[5].record()
         if record is not None:
             record.append(e)
         return s_if, s_neg
@@ -196,20 +217,20 @@ def run_b200(args):
     t_begin.record()
     for _ in range(args.steps):
         s_if, s_neg = step(rec)
-        if a.assembly == "rows" and L.ngsx_debug_get_timing(tbuf) == 0:      # waits for this step's assemble only
-            kern_ms.append(list(tbuf))
         if world > 1:                                    # the path's only exchange at this tier: scalar Integrate() all-reduce
             sc = torch.cat([s_if, s_neg])
             dist.all_reduce(sc)
     t_end.record()
     barrier()
+    if a.assembly == "rows" and L.ngsx_debug_get_timing(tbuf) == 0:          # mean over the timed steps (ring of 64 event sets)
+        kern_ms.append(list(tbuf))
     launches = L.ngsx_launch_count() - launches0
     L.ngsx_debug_set_timing(0)
     total_ms = t_begin.elapsed_time(t_end)
-    for e in rec:
+    for e in rec:                                        # per stage: from the start of the step to the stage's last kernel, on its stream
         stage_ms["classify"].append(e[0].elapsed_time(e[1]))
-        stage_ms["assemble"].append(e[1].elapsed_time(e[2]))
-        stage_ms["integrate"].append(e[2].elapsed_time(e[3]))
+        stage_ms["assemble"].append(e[1].elapsed_time(e[2]) if serial else e[0].elapsed_time(e[2]))
+        stage_ms["integrate"].append(e[2].elapsed_time(e[4]) if serial else max(e[0].elapsed_time(e[3]), e[0].elapsed_time(e[4])))
 
     # ---- e2e: level set from pinned host memory every step, CSR values + integrals back to the host ----------------
     h_lset = lsetp1.vec.cpu().pin_memory()
@@ -326,8 +347,9 @@ def run_b200(args):
                                f"assemble-to-CSR ({n_global} HASNEG elements) + CutInfo + Integrate(IF,NEG)",
                    "ne": mesh.ne, "hasneg_elements": n_global, "nnz": nnz_global, "assembly": a.assembly, "group": args.group, "colors": plan.ncolors,
                    "setup_s_untimed": round(setup_s, 2), "stage_ms": {"classify": cl_ms, "assemble": as_ms, "integrate": in_ms},
+                   "streams": "1 (serial stages)" if serial else "4: assemble | CutInfo.Update | Integrate(IF) | Integrate(NEG) overlap; stage_ms = start of step to the stage's last kernel",
                    "l2": "inputs larger than L2 (CSR values + pair descriptors + mesh > 1.4 GB touched per step vs 126 MB L2); no explicit flush",
-                   "partition": "owner-computes: contiguous chunks of the HASNEG element list per rank, a CSR row belongs to the rank of the first listed element touching it, halo elements re-evaluated, no interface-row exchange; element blocks for Integrate, scalars all-reduced (NCCL)"},
+                   "partition": "owner-computes: contiguous chunks of equal cost (cut element = 3.2 uncut) of the HASNEG element list per rank, a CSR row belongs to the rank of the first listed element touching it, halo elements re-evaluated, no interface-row exchange; element blocks for Integrate, scalars all-reduced (NCCL)"},
         "roofline": {"bound": "hbm", "kernel": "k_rows<10,6> (owner-computes row gather: every CSR value of the assembled operator written once)",
                      "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": traffic,
                      "peak_source": peak_src, "algorithmic_bytes_per_element": ALGO_BYTES_SCATTER,

@@ -1023,7 +1023,10 @@ static int launch_cutmat(const ElmatArgs &A, int fe_order, int sm_count, int64_t
 
 // optional per-kernel timing of the row-gather assembly (bench.py roofline): CUDA events on the launch stream
 static int g_timing = 0;
-static cudaEvent_t g_ev[4];
+constexpr int TIMING_RING = 64;
+static cudaEvent_t g_evr[TIMING_RING][4];
+static cudaEvent_t *g_ev = g_evr[0];
+static int g_ev_calls = 0;      // timed calls since the last ngsx_debug_get_timing
 static bool g_ev_ready = false;
 
 }  // namespace ngsx
@@ -1035,23 +1038,33 @@ extern "C" {
 // test hook: 0 disables the constant-rule path so both paths can be compared on the GPU
 void ngsx_debug_set_fast_path(int on) { g_use_fast = on; }
 
-// measurement hook: when on, ngsx_assemble_csr_rows_h1 records events around its kernels; ngsx_debug_get_timing waits for the
-// last call and returns {geometry factors (+ tables), cut-element matrices, row gather} in milliseconds
+// measurement hook: when on, ngsx_assemble_csr_rows_h1 records events around its kernels (a ring of 64 event sets, so the
+// caller need not synchronise every step); ngsx_debug_get_timing waits for the last call and returns the mean over the calls
+// since the previous read (at most the last 64) of {geometry factors (+ tables), cut-element matrices, row gather} in ms
 void ngsx_debug_set_timing(int on) {
   g_timing = on;
+  g_ev_calls = 0;
   if (on && !g_ev_ready) {
-    for (auto &e : g_ev) cudaEventCreate(&e);
+    for (auto &set : g_evr)
+      for (auto &e : set) cudaEventCreate(&e);
     g_ev_ready = true;
   }
 }
 int ngsx_debug_get_timing(double *h_ms) {
   NGSX_REQUIRE(h_ms && g_ev_ready, "debug_get_timing: timing was never enabled");
+  NGSX_REQUIRE(g_ev_calls > 0, "debug_get_timing: no timed call since the last read");
   NGSX_CUDA(cudaEventSynchronize(g_ev[3]));
-  for (int k = 0; k < 3; k++) {
-    float ms = 0.f;
-    NGSX_CUDA(cudaEventElapsedTime(&ms, g_ev[k], g_ev[k + 1]));
-    h_ms[k] = ms;
+  const int n = std::min(g_ev_calls, TIMING_RING);
+  for (int k = 0; k < 3; k++) h_ms[k] = 0.0;
+  for (int c = 0; c < n; c++) {
+    cudaEvent_t *set = g_evr[((g_ev_calls - 1 - c) % TIMING_RING + TIMING_RING) % TIMING_RING];
+    for (int k = 0; k < 3; k++) {
+      float ms = 0.f;
+      NGSX_CUDA(cudaEventElapsedTime(&ms, set[k], set[k + 1]));
+      h_ms[k] += ms / n;
+    }
   }
+  g_ev_calls = 0;
   return NGSX_OK;
 }
 
@@ -1113,7 +1126,7 @@ int ngsx_assemble_csr_rows_h1(const ngsx_mesh *mesh, const double *lset_v, int f
   fill_form(h_form, form);
   const int use_fast = g_use_fast && h_form->c_nitsche == 0.0 && h_form->c_dndn == 0.0 && dt != IF;
   // 1. reference tables (tiny), 2. geometry factors + quadrature work list, 3. cut-element matrices, 4. row gather
-  if (g_timing) cudaEventRecord(g_ev[0], st);
+  if (g_timing) { g_ev = g_evr[g_ev_calls % TIMING_RING]; g_ev_calls++; cudaEventRecord(g_ev[0], st); }
   switch (dim * 10 + fe_order) {
     case 21: launch_ref_tables<2, 1>(rv, nv, plan->tab, st); break;
     case 22: launch_ref_tables<2, 2>(rv, nv, plan->tab, st); break;

@@ -41,14 +41,22 @@ def element_block(ne: int, rank: int, world: int) -> Tuple[int, int]:
     return (ne * rank) // world, (ne * (rank + 1)) // world
 
 
-def row_owners(el2dof_active: torch.Tensor, ndof: int, world: int) -> torch.Tensor:
-    """owner[dof] = rank whose chunk of the active list holds the first element touching the dof; -1: untouched.  int32 [ndof]"""
+def row_owners(el2dof_active: torch.Tensor, ndof: int, world: int, weights: torch.Tensor = None) -> torch.Tensor:
+    """owner[dof] = rank whose chunk of the active list holds the first element touching the dof; -1: untouched.  int32 [ndof].
+    The list is cut into `world` contiguous chunks of equal element count, or of equal total weight when per-element cost
+    weights are given (cut elements cost ~3x an uncut one: quadrature block + row gather)"""
     n, nd = el2dof_active.shape
     dev = el2dof_active.device
     first = torch.full((ndof,), n, dtype=torch.int64, device=dev)
     idx = torch.arange(n, device=dev).repeat_interleave(nd)
     first.scatter_reduce_(0, el2dof_active.reshape(-1).long(), idx, reduce="amin")
-    owner = torch.div(first * world, max(n, 1), rounding_mode="floor")
+    if weights is None:
+        owner = torch.div(first * world, max(n, 1), rounding_mode="floor")
+    else:
+        w = weights.to(torch.float64)
+        before = torch.cumsum(w, 0) - w                                  # weight in front of each list position
+        rank_of_pos = torch.clamp((before * (world / float(w.sum()))).floor().long(), max=world - 1)
+        owner = rank_of_pos[torch.clamp(first, max=max(n - 1, 0))]
     return torch.where(first < n, owner, torch.full_like(owner, -1)).to(torch.int32)
 
 
