@@ -172,7 +172,7 @@ def run_b200(args):
     side = [torch.cuda.Stream() for _ in range(3)]
     serial = world > 1 or bool(os.environ.get("NGSX_BENCH_SERIAL"))      # NGSX_BENCH_SERIAL: A/B switch at N = 1
 
-    def step(record):
+    def step(record, serial=serial):
         e = [ev() for _ in range(6)]
         e[0].record()
         if serial:
@@ -231,6 +231,23 @@ def run_b200(args):
         stage_ms["classify"].append(e[0].elapsed_time(e[1]))
         stage_ms["assemble"].append(e[1].elapsed_time(e[2]) if serial else e[0].elapsed_time(e[2]))
         stage_ms["integrate"].append(e[2].elapsed_time(e[4]) if serial else max(e[0].elapsed_time(e[3]), e[0].elapsed_time(e[4])))
+
+    # stage / kernel breakdown without overlap: a few serial steps after the timed region (reported beside the overlapped figures)
+    serial_break = None
+    if not serial:
+        rec_s = []
+        L.ngsx_debug_set_timing(1)
+        for _ in range(5):
+            step(rec_s, True)
+        torch.cuda.synchronize()
+        ks = list(tbuf) if L.ngsx_debug_get_timing(tbuf) == 0 else None
+        ks = list(tbuf) if ks is not None else None
+        L.ngsx_debug_set_timing(0)
+        serial_break = {"classify": statistics.mean(e[0].elapsed_time(e[1]) for e in rec_s),
+                        "assemble": statistics.mean(e[1].elapsed_time(e[2]) for e in rec_s),
+                        "integrate": statistics.mean(e[2].elapsed_time(e[4]) for e in rec_s),
+                        "step": statistics.mean(e[0].elapsed_time(e[5]) for e in rec_s),
+                        "kernel_ms": None if ks is None else {"k_geom": ks[0], "k_cutmat": ks[1], "k_rows": ks[2]}}
 
     # ---- e2e: level set from pinned host memory every step, CSR values + integrals back to the host ----------------
     h_lset = lsetp1.vec.cpu().pin_memory()
@@ -347,6 +364,7 @@ def run_b200(args):
                                f"assemble-to-CSR ({n_global} HASNEG elements) + CutInfo + Integrate(IF,NEG)",
                    "ne": mesh.ne, "hasneg_elements": n_global, "nnz": nnz_global, "assembly": a.assembly, "group": args.group, "colors": plan.ncolors,
                    "setup_s_untimed": round(setup_s, 2), "stage_ms": {"classify": cl_ms, "assemble": as_ms, "integrate": in_ms},
+                   "stage_ms_one_stream": serial_break,
                    "streams": "1 (serial stages)" if serial else "4: assemble | CutInfo.Update | Integrate(IF) | Integrate(NEG) overlap; stage_ms = start of step to the stage's last kernel",
                    "l2": "inputs larger than L2 (CSR values + pair descriptors + mesh > 1.4 GB touched per step vs 126 MB L2); no explicit flush",
                    "partition": "owner-computes: contiguous chunks of equal cost (cut element = 3.2 uncut) of the HASNEG element list per rank, a CSR row belongs to the rank of the first listed element touching it, halo elements re-evaluated, no interface-row exchange; element blocks for Integrate, scalars all-reduced (NCCL)"},
