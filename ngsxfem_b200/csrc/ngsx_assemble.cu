@@ -1127,13 +1127,16 @@ int ngsx_assemble_csr_rows_h1(const ngsx_mesh *mesh, const double *lset_v, int f
   const int use_fast = g_use_fast && h_form->c_nitsche == 0.0 && h_form->c_dndn == 0.0 && dt != IF;
   // 1. reference tables (tiny), 2. geometry factors + quadrature work list, 3. cut-element matrices, 4. row gather
   if (g_timing) { g_ev = g_evr[g_ev_calls % TIMING_RING]; g_ev_calls++; cudaEventRecord(g_ev[0], st); }
-  switch (dim * 10 + fe_order) {
-    case 21: launch_ref_tables<2, 1>(rv, nv, plan->tab, st); break;
-    case 22: launch_ref_tables<2, 2>(rv, nv, plan->tab, st); break;
-    case 31: launch_ref_tables<3, 1>(rv, nv, plan->tab, st); break;
-    case 32: launch_ref_tables<3, 2>(rv, nv, plan->tab, st); break;
+  if (plan->tab_rule != rv || plan->tab_key != dim * 1000 + fe_order * 100 + nv) {      // calls on one plan are stream-ordered by the caller
+    switch (dim * 10 + fe_order) {
+      case 21: launch_ref_tables<2, 1>(rv, nv, plan->tab, st); break;
+      case 22: launch_ref_tables<2, 2>(rv, nv, plan->tab, st); break;
+      case 31: launch_ref_tables<3, 1>(rv, nv, plan->tab, st); break;
+      case 32: launch_ref_tables<3, 2>(rv, nv, plan->tab, st); break;
+    }
+    NGSX_LAUNCH_CHECK();
+    plan->tab_rule = rv; plan->tab_key = dim * 1000 + fe_order * 100 + nv;
   }
-  NGSX_LAUNCH_CHECK();
   NGSX_CUDA(cudaMemsetAsync(plan->cutcount, 0, sizeof(int32_t), st));
   auto *e = reinterpret_cast<unsigned long long *>(err);
   const unsigned nb = (unsigned)((nlist + 255) / 256);

@@ -30,6 +30,8 @@ struct ngsx_rowplan {
   int32_t *cutcount = nullptr;      // [1]
   double *cutmats = nullptr;        // [nlist][nd*nd]
   double *tab = nullptr;            // [(npair+1)][nd*nd] reference tables of the constant-rule path
+  const void *tab_rule = nullptr;   // rule the tables were computed for (they depend on the reference rule only: computed once)
+  int tab_key = 0;
 };
 
 namespace ngsx {
