@@ -203,6 +203,12 @@ int ngsx_assemble_csr_rows_h1(const ngsx_mesh *mesh, const double *lset_v, int f
  * blocks of the plan's list entries (elements, or facet patches with their merged dof lists) are gathered row by row;
  * accumulate as above.  nd in {3, 4, 5, 6, 8, 9, 10, 12, 14, 20}. */
 int ngsx_assemble_csr_rows_mats(ngsx_rowplan *plan, const double *mats, int accumulate, double *vals, void *stream);
+/* The same for vectors (AddElementVector, NGS/comp/linearform.cpp:209-243, without atomics): out[d] (+)= scale * sum of
+ * src[pairs[p]] over p in [dofptr[d], dofptr[d+1]), in list order.  src: flattened element vectors (e.g. of ngsx_elvec_h1),
+ * pairs: indices into it grouped by dof -- entries a sign mask removes (DiffOpX, xfem/xfemdiffops.cpp:30-40) are simply not
+ * listed.  Bitwise reproducible. */
+int ngsx_gather_vec(int64_t ndof, const int64_t *dofptr /*[ndof+1]*/, const int64_t *pairs, const double *src, double scale,
+                    int accumulate, double *out, void *stream);
 
 /* ---- Integrate ------------------------------------------------------------------------------------------------- */
 /* out[0] = sum_e sum_q |det J_e| w_q f(x_q) over the (dt, order) cut rule; fixed-shape tree reduction (bitwise

@@ -132,9 +132,30 @@ static int launch_rows_mats_t(const RowMatArgs &A, int sm_count, cudaStream_t st
   return NGSX_OK;
 }
 
+// vectors: thread per dof, contributions summed in list order
+__global__ void __launch_bounds__(256) k_gather_vec(int64_t ndof, const int64_t *__restrict__ dofptr, const int64_t *__restrict__ pairs,
+                                                   const double *__restrict__ src, double scale, int accumulate, double *__restrict__ out) {
+  const int64_t d = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (d >= ndof) return;
+  const int64_t a = dofptr[d], b = dofptr[d + 1];
+  if (a == b && accumulate) return;
+  double s = 0.0;
+  for (int64_t p = a; p < b; p++) s += __ldg(src + __ldg(pairs + p));
+  out[d] = accumulate ? out[d] + scale * s : scale * s;
+}
+
 }  // namespace ngsx
 
 using namespace ngsx;
+
+extern "C" int ngsx_gather_vec(int64_t ndof, const int64_t *dofptr, const int64_t *pairs, const double *src, double scale, int accumulate,
+                               double *out, void *stream) {
+  NGSX_REQUIRE(ndof >= 0 && (ndof == 0 || (dofptr && out)), "gather_vec: bad arguments");
+  if (ndof == 0) return NGSX_OK;
+  k_gather_vec<<<(unsigned)((ndof + 255) / 256), 256, 0, as_stream(stream)>>>(ndof, dofptr, pairs, src, scale, accumulate, out);
+  NGSX_LAUNCH_CHECK();
+  return NGSX_OK;
+}
 
 extern "C" int ngsx_assemble_csr_rows_mats(ngsx_rowplan *plan, const double *mats, int accumulate, double *vals, void *stream) {
   NGSX_REQUIRE(plan, "assemble_csr_rows_mats: plan is NULL");

@@ -304,10 +304,17 @@ class SymbolicCutLFI:
         if VOL_or_BND != VOL or element_boundary or skeleton or time_order >= 0 or subdivlvl != 0 or deformation is not None:
             raise NgsxError(-2, "this SymbolicCutLFI variant is outside the CUDA path")
         self.lset, self.dt, self.force_intorder, self.definedonelements = lset, int(domain_type), force_intorder, definedonelements
-        # form = f * v with f a polynomial CoefficientFunction (py_tutorials/fictdom_ghostpen.py:98: coeff_f*v)
-        if not isinstance(form, Expr) or len(form.terms) != 1 or form.terms[0][1] != 0 or form.terms[0][2] != ("v",):
-            raise NgsxError(-2, "SymbolicCutLFI: form must be f*v with a polynomial f; no CPU fallback")
-        self.coef = (form.poly if form.poly is not None else Poly({(0, 0, 0): 1.0})) * form.terms[0][0]
+        # form = f * v with f a polynomial CoefficientFunction (py_tutorials/fictdom_ghostpen.py:98: coeff_f*v); on [Vh, Vhx]
+        # f * (v_std + neg(v_x)) etc. (py_tutorials/nxfem.py:109-110): one scalar per test block {std, x NEG-masked, x POS-masked}
+        names = {("v",): 0, ("xvn",): 1, ("xvp",): 2}
+        if not isinstance(form, Expr) or not form.terms or any(p != 0 or a not in names for _, p, a in form.terms):
+            raise NgsxError(-2, "SymbolicCutLFI: form must be f*v (f*(v + neg(v_x)) on [Vh, Vhx]) with a polynomial f; no CPU fallback")
+        self.blocks = [0.0, 0.0, 0.0]
+        for c, _, a in form.terms:
+            self.blocks[names[a]] += c
+        self.poly = form.poly if form.poly is not None else Poly({(0, 0, 0): 1.0})
+        self.coef = self.poly * self.blocks[0]
+        self.has_x = self.blocks[1] != 0.0 or self.blocks[2] != 0.0
 
     def intorder(self, fe_order):
         return self.force_intorder if self.force_intorder >= 0 else 2 * fe_order       # xfem/symboliccutlfi.cpp:85
@@ -705,39 +712,83 @@ class RestrictedBilinearForm(BilinearForm):
 class LinearForm:
     group_size = 6
 
-    def __init__(self, space: H1):
+    def __init__(self, space):
+        from .xfes import CompoundFESpace
         self.space = space
+        self.compound = isinstance(space, CompoundFESpace)
+        self._h1 = space.std if self.compound else space
         self.integrators: List[SymbolicCutLFI] = []
         self.vec = torch.zeros(space.ndof, dtype=torch.float64, device=space.mesh.device)
         self._plans: Dict[int, _Plan] = {}
+        self._xplans: Dict[int, tuple] = {}
 
     def __iadd__(self, integ):
         if not isinstance(integ, SymbolicCutLFI):
             raise NgsxError(-2, "only SymbolicCutLFI integrators are on the CUDA path")
+        if integ.has_x and not self.compound:
+            raise NgsxError(-1, "neg / pos test functions need a LinearForm on FESpace([Vh, XFESpace])")
         self.integrators.append(integ)
         return self
 
     def Assemble(self):
         """NGS/comp/linearform.cpp:209-243"""
         L = _lib_()
-        fes = self.space
+        fes = self._h1
+        if self.vec.numel() != self.space.ndof:                            # XFESpace.Update changed the number of x-dofs
+            self.vec = torch.zeros(self.space.ndof, dtype=torch.float64, device=fes.mesh.device)
+            self._xplans.clear()
         self.vec.zero_()
         for k, integ in enumerate(self.integrators):
-            if k not in self._plans:
-                ci = CutInfo(fes.mesh, integ.lset)
-                ba = ci.GetElementsOfType({NEG: HASNEG, POS: HASPOS, IF: CDOM_IF}[integ.dt])
-                if integ.definedonelements is not None:
-                    ba = ba & integ.definedonelements
-                els = ba.nonzero()
-                table = fes.el2dof[els].contiguous()
-                perm, cptr = color_list(table, fes.ndof, self.group_size)
-                self._plans[k] = _Plan(els[perm].to(torch.int32).contiguous(), table[perm].contiguous(), cptr, self.group_size)
-            plan = self._plans[k]
-            poly = _poly_of(integ.coef)
-            check(L.ngsx_assemble_vec_h1(ctypes.byref(fes.mesh.c_struct()), _ptr(_lset_vec(integ.lset)), fes.order, integ.dt,
-                                         integ.intorder(fes.order), ctypes.byref(poly), plan.els.numel(), _ptr(plan.els), _ptr(plan.table),
-                                         plan.ncolors, plan.h_color_ptr, plan.group, _ptr(self.vec), _stream()))
+            if integ.blocks[0] != 0.0:
+                if k not in self._plans:
+                    ci = CutInfo(fes.mesh, integ.lset)
+                    ba = ci.GetElementsOfType({NEG: HASNEG, POS: HASPOS, IF: CDOM_IF}[integ.dt])
+                    if integ.definedonelements is not None:
+                        ba = ba & integ.definedonelements
+                    els = ba.nonzero()
+                    table = fes.el2dof[els].contiguous()
+                    perm, cptr = color_list(table, fes.ndof, self.group_size)
+                    self._plans[k] = _Plan(els[perm].to(torch.int32).contiguous(), table[perm].contiguous(), cptr, self.group_size)
+                plan = self._plans[k]
+                poly = _poly_of(integ.coef)
+                check(L.ngsx_assemble_vec_h1(ctypes.byref(fes.mesh.c_struct()), _ptr(_lset_vec(integ.lset)), fes.order, integ.dt,
+                                             integ.intorder(fes.order), ctypes.byref(poly), plan.els.numel(), _ptr(plan.els), _ptr(plan.table),
+                                             plan.ncolors, plan.h_color_ptr, plan.group, _ptr(self.vec), _stream()))
+            if integ.has_x:
+                self._assemble_x(integ, k)
         return self
+
+    def _assemble_x(self, integ, k):
+        """x-dof part (DiffOpX<RNEG/RPOS> as test operator, xfem/xfemdiffops.cpp:30-40): the element vectors of the IF elements
+        (the only ones with x-dofs), gathered per x-dof over the entries whose sign matches the operator -- fixed order, no atomics"""
+        L = _lib_()
+        x, fes = self.space.x, self._h1
+        nd = fes.nd
+        if k not in self._xplans:
+            keep = torch.ones(x.if_els.numel(), dtype=torch.bool, device=x.if_els.device)
+            if integ.definedonelements is not None:
+                keep = integ.definedonelements.to_bool()[x.if_els.long()]
+            plans = []
+            for blk, sign in ((1, NEG), (2, POS)):
+                if integ.blocks[blk] == 0.0:
+                    continue
+                sel = ((x.xsign == sign) & keep[:, None]).reshape(-1)
+                src = torch.nonzero(sel).reshape(-1)                                       # index into the flattened [nIF][nd] vectors
+                dof = x.el2dofs.reshape(-1)[src].long()
+                order = torch.argsort(dof * (x.if_els.numel() * nd) + src)                 # by x-dof, then by (element, local dof)
+                dofptr = torch.zeros(x.ndof + 1, dtype=torch.int64, device=src.device)
+                dofptr[1:] = torch.cumsum(torch.bincount(dof, minlength=x.ndof), 0)
+                plans.append((integ.blocks[blk], dofptr, src[order].contiguous()))
+            self._xplans[k] = (plans, torch.empty((x.if_els.numel(), nd), dtype=torch.float64, device=x.if_els.device))
+        plans, elvecs = self._xplans[k]
+        if x.if_els.numel() == 0:
+            return
+        poly = _poly_of(integ.poly)
+        check(L.ngsx_elvec_h1(ctypes.byref(fes.mesh.c_struct()), _ptr(_lset_vec(integ.lset)), fes.order, integ.dt, integ.intorder(fes.order),
+                              ctypes.byref(poly), x.if_els.numel(), _ptr(x.if_els), _ptr(elvecs), None, _stream()))
+        xvec = self.vec[fes.ndof:]
+        for scale, dofptr, pairs in plans:
+            check(L.ngsx_gather_vec(x.ndof, _ptr(dofptr), _ptr(pairs), _ptr(elvecs), float(scale), 1, _ptr(xvec), _stream()))
 
 
 # XFESpace and the sign-masked operators (xfem/python_xfem.cpp:321-448, python/__init__.py:22-105, 397-409)

@@ -75,3 +75,24 @@ def nxfem_elmat(dim, order, vnums, pmat, ls, xsign, kappa_neg, alpha, stab_facto
         jump = U[NEG] - U[POS]
         A += meas * w[q] * (np.outer(jump, flux) + np.outer(flux, jump) + stab * np.outer(jump, jump))
     return A if xsign is not None else A[:nd, :nd]
+
+
+def nxfem_elvec(dim, order, vnums, pmat, ls, xsign, dt, fpoly):
+    """compound element vector (2 nd) of SymbolicLFI(levelset_domain = dt, form = f * (v_std + op(v_x))), op = neg for dt = NEG,
+    pos for dt = POS (py_tutorials/nxfem.py:109-110; xfem/symboliccutlfi.cpp:52-158, intorder = 2 order :85).
+    fpoly: {(ex, ey, ez): coef}.  xsign = None: uncut element (block nd)."""
+    J = (pmat[:dim] - pmat[dim]).T
+    meas = abs(np.linalg.det(J))
+    nd = orc.load().orc_h1_ndof(dim, order)
+    xs = [-1] * nd if xsign is None else xsign
+    b = np.zeros(2 * nd)
+    npt, pts, w = orc.cut_rule(dim, pmat, ls, dt, 2 * order)
+    m = (np.asarray(xs) == dt).astype(float)
+    for q in range(max(npt, 0)):
+        xi = pts[q][:dim]
+        s, _ = orc.h1_shape(dim, order, vnums, xi)
+        x = np.zeros(3)
+        x[:dim] = pmat[dim] + J @ xi
+        f = sum(c * x[0] ** e[0] * x[1] ** e[1] * x[2] ** e[2] for e, c in fpoly.items())
+        b += meas * w[q] * f * np.concatenate([s, m * s])
+    return b if xsign is not None else b[:nd]

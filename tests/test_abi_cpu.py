@@ -150,3 +150,25 @@ def test_xfem_form_expansion():
         xfes.xterms_of(k0 * k0 * u[0] * v[0])
     with pytest.raises(_lib.NgsxError):
         xfes.neg(u_std)
+
+
+def test_xfem_linearform_parse():
+    """f-2 host logic: f * (v_std + neg(v_x)) (py_tutorials/nxfem.py:109-110) -> one scalar per test block and the polynomial f;
+    intorder = 2 order (xfem/symboliccutlfi.cpp:85); forms with a trial function or a power of h are refused"""
+    import pytest
+    from ngsxfem_b200 import ngs, xfem, xfes
+    from ngsxfem_b200._lib import NgsxError
+    from ngsxfem_b200.ngs import Expr
+    v_std, v_x = Expr.atom("v"), xfes.XProxy("v")
+    f0 = 1.5 + ngs.x * ngs.y
+    li = xfem.SymbolicLFI(levelset_domain={"levelset": None, "domain_type": xfem.NEG}, form=f0 * (v_std + xfes.neg(v_x)))
+    assert li.blocks == [1.0, 1.0, 0.0] and li.has_x and li.intorder(2) == 4
+    assert li.poly.terms == {(0, 0, 0): 1.5, (1, 1, 0): 1.0}
+    lp = xfem.SymbolicLFI(levelset_domain={"levelset": None, "domain_type": xfem.POS}, form=2.0 * (v_std + xfes.pos(v_x)))
+    assert lp.blocks == [2.0, 0.0, 2.0]
+    plain = xfem.SymbolicLFI(levelset_domain={"levelset": None, "domain_type": xfem.NEG}, form=f0 * v_std)
+    assert plain.blocks == [1.0, 0.0, 0.0] and not plain.has_x
+    with pytest.raises(NgsxError):
+        xfem.SymbolicLFI(levelset_domain={"levelset": None, "domain_type": xfem.NEG}, form=Expr.atom("u") * v_std)
+    with pytest.raises(NgsxError):
+        xfem.SymbolicLFI(levelset_domain={"levelset": None, "domain_type": xfem.NEG}, form=ngs.specialcf.mesh_size * v_std)

@@ -448,6 +448,61 @@ def test_xfem_nitsche_compound(X, dim, fo):
 
 
 @pytest.mark.parametrize("dim,fo", [(2, 1), (2, 2), (3, 1), (3, 2)])
+def test_xfem_linearform_compound(X, dim, fo):
+    """f-2: right-hand side of py_tutorials/nxfem.py:108-110 on FESpace([Vh, XFESpace(Vh)]): f0 (v_std + neg(v_x)) on NEG plus
+    f1 (v_std + pos(v_x)) on POS with polynomial f, vs the numpy restatement (oracle/xfem_ref.py:nxfem_elvec); bitwise reproducible."""
+    from oracle import orc, xfem_ref
+    from ngsxfem_b200.xfes import FESpace
+    xf, ngs = X.xfem, X.ngs
+    if dim == 2:
+        mesh = ngs.Mesh(X.meshes.MakeStructured2DMesh(7, lo=(-1.5, -1.5), hi=(1.5, 1.5)))
+        lset = ngs.SphereLevelset((0.05, -0.02), 1.0)
+        f0 = 1.5 + ngs.x * ngs.y
+        p0 = {(0, 0, 0): 1.5, (1, 1, 0): 1.0}
+    else:
+        mesh = ngs.Mesh(X.meshes.MakeStructured3DMesh(6))
+        lset = ngs.SphereLevelset((0.52, 0.49, 0.51), 0.41)
+        f0 = 1.5 + ngs.x * ngs.z
+        p0 = {(0, 0, 0): 1.5, (1, 0, 1): 1.0}
+    f1 = 2.0 - ngs.y * ngs.y
+    p1 = {(0, 0, 0): 2.0, (0, 2, 0): -1.0}
+    gf = ngs.GridFunction(ngs.H1(mesh, order=1))
+    xf.InterpolateToP1(lset, gf)
+    ci = xf.CutInfo(mesh, gf)
+    Vh = ngs.H1(mesh, order=fo)
+    Vhx = xf.XFESpace(Vh, ci)
+    VhG = FESpace([Vh, Vhx])
+    v_std, v_x = VhG.TestFunction()
+    v = [v_std + op(v_x) for op in (xf.neg, xf.pos)]
+    f = xf.LinearForm(VhG)
+    f += xf.SymbolicLFI(levelset_domain={"levelset": gf, "domain_type": NEG}, form=f0 * v[0])
+    f += xf.SymbolicLFI(levelset_domain={"levelset": gf, "domain_type": POS}, form=f1 * v[1])
+    f.Assemble()
+    first = f.vec.clone()
+    f.Assemble()
+    assert torch.equal(first[Vh.ndof:], f.vec[Vh.ndof:])                    # the x-dof gather has a fixed summation order
+    el2v, vert, ls, e2d = mesh.el2v.cpu().numpy(), mesh.vert.cpu().numpy(), gf.vec.cpu().numpy(), Vh.el2dof.cpu().numpy()
+    dom, ratio, nerr = orc.cutinfo_mesh(dim, el2v, vert, ls)
+    b2x, dod = xfem_ref.xfespace(dim, fo, el2v, e2d, Vh.ndof, mesh.nv, dom)
+    ref = np.zeros(VhG.ndof)
+    for e in range(mesh.ne):
+        pm, l = vert[el2v[e]], ls[el2v[e]]
+        for dt, fp in ((0, p0), (1, p1)):
+            if dom[e] == 2:
+                xs = dod[b2x[e2d[e]]]
+                ev = xfem_ref.nxfem_elvec(dim, fo, el2v[e], pm, l, xs, dt, fp)
+                d = np.concatenate([e2d[e], Vh.ndof + b2x[e2d[e]]])
+            elif dom[e] == dt:
+                ev = xfem_ref.nxfem_elvec(dim, fo, el2v[e], pm, l, None, dt, fp)
+                d = e2d[e]
+            else:
+                continue
+            np.add.at(ref, d, ev)
+    got = f.vec.cpu().numpy()
+    assert np.abs(ref[Vh.ndof:]).max() > 0 and abs(got - ref).max() <= 1e-12 * abs(ref).max()
+
+
+@pytest.mark.parametrize("dim,fo", [(2, 1), (2, 2), (3, 1), (3, 2)])
 def test_tracefem_operator(X, dim, fo):
     """config 4: TraceFEM Laplace-Beltrami operator, interface mass + tangential stiffness P grad(u).P grad(v), P = I - n n^T
     (py_tutorials/tracefem3d.py:70-88) on the IF elements + ghost-penalty facet patches between IF elements; vs a numpy
