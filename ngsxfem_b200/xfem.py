@@ -490,9 +490,13 @@ class BilinearForm:
             els = torch.nonzero(de).reshape(-1) if els is None else els[de[els]]
         if els is None:
             els = torch.arange(self.space.mesh.ne, device=self.space.mesh.device)
-        if integ.xterms is not None:                               # the IF elements go through the compound kernel
-            cut = self.space.x.cutinfo.GetElementsOfType(IF).to_bool()
-            els = els[~cut[els]]
+        if integ.xterms is not None:
+            # the IF elements go through the compound kernel, and this plan is tied to the XFESpace's cut state anyway (it is
+            # rebuilt with it): list only the uncut elements of the integrator's own domain instead of re-classifying all
+            cdt = {NEG: CDOM_NEG, POS: CDOM_POS}.get(integ.dt)
+            if cdt is None:
+                return els[:0]
+            els = els[self.space.x.cutinfo.GetElementsOfType(cdt).to_bool()[els]]
         return els
 
     def _x_plan(self, integ: SymbolicCutBFI):
