@@ -263,10 +263,11 @@ typedef struct ngsx_xterm {
 /* mats [nlist][2 nd][2 nd] row-major over [dofs of Vh | x-dofs] of each listed element (rows = test functions): the block
  * CalcElementMatrixAdd (xfem/symboliccutbfi.cpp:73-315) produces on a CompoundFiniteElement(H1 element, XFiniteElement).
  * xsign [nlist][nd] int8: XFESpace::domofdof (NEG/POS) of the x-dof over local dof i (xfem/xFESpace.cpp:346-366);
- * ratio [ne]: cut ratios of ngsx_classify.  Elements whose (dt) rule is empty give a zero block. */
+ * ratio [ne]: cut ratios of ngsx_classify.  Elements whose (dt) rule is empty give a zero block.  accumulate != 0: the block
+ * is added to mats (several integrators of one form share one buffer and one gather). */
 int ngsx_xfem_elmat_h1(const ngsx_mesh *mesh, const double *lset_v, int fe_order, int dt, int intorder, int32_t nterms,
                        const ngsx_xterm *h_terms, int64_t nlist, const int32_t *els, const int8_t *xsign, const double *ratio,
-                       double *mats, void *stream);
+                       int accumulate, double *mats, void *stream);
 
 /* Merged patch blocks for the row gather (NGSolve's compressed_dnums / compressed_elmat, NGS/comp/bilinearform.cpp:1800-1853).
  * ngsx_facetpatch_table_h1 (symbolic, synchronises): table [np][ndp] = dofs of element 0, then the dofs of element 1 that

@@ -83,7 +83,7 @@ SIGNATURES = {
     "ngsx_dofs_of_elements": (c_int, [c_i64, c_i32, c_void_p, c_void_p, c_i64, c_void_p, c_void_p]),
     "ngsx_facetpatch_elmat_h1": (c_int, [ctypes.POINTER(Mesh), c_int, c_double, c_int, c_i64, c_void_p, c_void_p, c_void_p]),
     "ngsx_xfem_elmat_h1": (c_int, [ctypes.POINTER(Mesh), c_void_p, c_int, c_int, c_int, c_i32, ctypes.POINTER(XTerm), c_i64, c_void_p, c_void_p,
-                                   c_void_p, c_void_p, c_void_p]),
+                                   c_void_p, c_int, c_void_p, c_void_p]),
     "ngsx_st_rule_count": (c_int, [ctypes.POINTER(Mesh), c_void_p, c_int, c_int, c_int, c_int, c_void_p, c_void_p]),
     "ngsx_st_rule_fill": (c_int, [ctypes.POINTER(Mesh), c_void_p, c_int, c_int, c_int, c_int, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p]),
     "ngsx_st_integrate": (c_int, [ctypes.POINTER(Mesh), c_void_p, c_int, c_int, c_int, c_int, ctypes.POINTER(Poly), ctypes.POINTER(c_i32),

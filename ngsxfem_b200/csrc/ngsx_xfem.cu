@@ -8,16 +8,13 @@
 //   M_ij = int phi_i phi_j,  N_ij = int phi_i dn phi_j,  D_ij = int dn phi_i dn phi_j,  K_ij = int grad phi_i . grad phi_j,
 // (n = grad lset / |grad lset|, elementwise constant for a P1 level set), so the kernel integrates the base matrices once and
 // then forms the (2 nd) x (2 nd) compound block  [std dofs | x dofs]  by mask algebra.
-// One warp per listed element: lane q evaluates quadrature point q of a round into shared memory, the nd^2 entries of each
-// base matrix are spread over the lanes; the compound block leaves as coalesced stores.  The blocks are scattered by the
-// owner-computes gather (ngsx_assemble_csr_rows_mats).
+// The blocks are scattered by the owner-computes gather (ngsx_assemble_csr_rows_mats); several integrators of one form sum
+// their blocks in one buffer (accumulate) and share one gather.
 #include <algorithm>
 #include "ngsx_host.cuh"
 
 namespace ngsx {
 
-constexpr int XW = 4;             // warps per CTA
-constexpr int XQ = 16;            // quadrature points staged per round
 constexpr int XMAXTERMS = 32;
 
 struct XTermsDev {
@@ -45,34 +42,135 @@ __device__ __forceinline__ double xipow(double x, int p) {
   return r;
 }
 
+// ---------------------------------------------------------------------------------------------------------------
+// ONE THREAD PER ELEMENT, from monomial moments (as k_cutmat_mom, ngsx_assemble.cu): the hierarchical
+// shapes are lam_i and -1/2 lam_a lam_b, so all four base matrices are fixed combinations of the moments int lam^alpha over
+// the cut part (degree <= 4), of g_c = grad lam_c . n and of the Gram matrix grad lam_a . grad lam_b.  Per rule point the
+// thread accumulates the 60 moments; per element it folds the form's terms into 5 coefficients per block class
+// (shared memory, 45 doubles per thread), parks the moments in its shared-memory slice (runtime-indexed by the expansion
+// loops: fully unrolled, the 400 entries of a 3D P2 block spilled 3.8 KB per thread) and writes the (2 nd)^2 block entry by
+// entry.  The first version -- a warp per element staging shape values of 16 points through shared memory, lanes = entries --
+// took 0.69-0.77 ms per integrator for 93 120 P2 tets; this one 0.38 ms (0.53 with accumulate), bound by its 4 warps per SM.
+// ---------------------------------------------------------------------------------------------------------------
+#ifndef NGSX_XMT
+#define NGSX_XMT 128
+#endif
+constexpr int XMT = NGSX_XMT;     // threads per CTA of the moment kernel (120 doubles of shared memory per thread: one CTA per SM; 64 x 3 measured no better)
+constexpr int XCO = 45;           // 9 classes x 5 operator pairs (odd stride: conflict-free)
+
+// moments + geometry of one element in the thread's shared-memory slice (runtime-indexed by the expansion loops)
 template <int DIM, int ORDER>
-__global__ void __launch_bounds__(XW * 32) k_xfem(ngsx_mesh M, const double *__restrict__ lset, const CutTable *__restrict__ tab, int dt,
-                                                  const double4 *__restrict__ rule_vol, int nr_vol, const double4 *__restrict__ rule_if, int nr_if,
-                                                  XTermsDev X, int64_t nlist, const int32_t *__restrict__ els, const int8_t *__restrict__ xsign,
-                                                  const double *__restrict__ ratio, double *__restrict__ mats) {
-  constexpr int ND = H1<DIM, ORDER>::ND, NE = ND * ND, N2 = 2 * ND, T = (NE + 31) / 32;
+struct XMom {
+  static constexpr int ND = H1<DIM, ORDER>::ND, NV = DIM + 1, NEDGE = ND - NV, N2 = NV * (NV + 1) / 2;
+  static constexpr int NT = NEDGE > 0 ? NEDGE : 1, NQ = NEDGE > 0 ? NEDGE * (NEDGE + 1) / 2 : 1;
+  static constexpr int O_M1 = 1, O_M2 = O_M1 + NV, O_MT = O_M2 + N2, O_MQ = O_MT + NV * NT, O_G = O_MQ + NQ, O_GM = O_G + NV;
+  static constexpr int TOT = (O_GM + N2) | 1;                          // odd stride: conflict-free
+  const double *w;
+  __device__ __forceinline__ static int sym(int a, int b) { return a >= b ? a * (a + 1) / 2 + b : b * (b + 1) / 2 + a; }
+  __device__ __forceinline__ double m0() const { return w[0]; }
+  __device__ __forceinline__ double m1(int a) const { return w[O_M1 + a]; }
+  __device__ __forceinline__ double m2(int a, int b) const { return w[O_M2 + sym(a, b)]; }
+  __device__ __forceinline__ double mT(int v, int ed) const { return w[O_MT + v * NT + ed]; }
+  __device__ __forceinline__ double mQ(int a, int b) const { return w[O_MQ + sym(a, b)]; }
+  __device__ __forceinline__ double g(int a) const { return w[O_G + a]; }
+  __device__ __forceinline__ double gg(int a, int b) const { return w[O_GM + sym(a, b)]; }
+  // int phi_i phi_j
+  __device__ __forceinline__ double M(int i, int j) const {
+    if (i < NV && j < NV) return m2(i, j);
+    if (i < NV) return -0.5 * mT(i, j - NV);
+    if (j < NV) return -0.5 * mT(j, i - NV);
+    return 0.25 * mQ(i - NV, j - NV);
+  }
+  // int phi_i dn phi_j
+  __device__ __forceinline__ double N(int i, int j) const {
+    if (i < NV && j < NV) return g(j) * m1(i);
+    if (i < NV) {
+      int a, b;
+      edge_vertices<DIM>(j - NV, a, b);
+      return -0.5 * (g(a) * m2(i, b) + g(b) * m2(i, a));
+    }
+    int a, b;
+    edge_vertices<DIM>(i - NV, a, b);
+    if (j < NV) return -0.5 * g(j) * m2(a, b);
+    int c, d;
+    edge_vertices<DIM>(j - NV, c, d);
+    return 0.25 * (g(c) * mT(d, i - NV) + g(d) * mT(c, i - NV));
+  }
+  // int dn phi_i dn phi_j
+  __device__ __forceinline__ double D(int i, int j) const {
+    if (i < NV && j < NV) return g(i) * g(j) * m0();
+    if (i < NV || j < NV) {
+      const int v = i < NV ? i : j, ed = (i < NV ? j : i) - NV;
+      int a, b;
+      edge_vertices<DIM>(ed, a, b);
+      return -0.5 * g(v) * (g(a) * m1(b) + g(b) * m1(a));
+    }
+    int a, b, c, d;
+    edge_vertices<DIM>(i - NV, a, b);
+    edge_vertices<DIM>(j - NV, c, d);
+    return 0.25 * (g(a) * g(c) * m2(b, d) + g(a) * g(d) * m2(b, c) + g(b) * g(c) * m2(a, d) + g(b) * g(d) * m2(a, c));
+  }
+  // int grad phi_i . grad phi_j
+  __device__ __forceinline__ double K(int i, int j) const {
+    if (i < NV && j < NV) return gg(i, j) * m0();
+    if (i < NV || j < NV) {
+      const int v = i < NV ? i : j, ed = (i < NV ? j : i) - NV;
+      int a, b;
+      edge_vertices<DIM>(ed, a, b);
+      return -0.5 * (gg(v, a) * m1(b) + gg(v, b) * m1(a));
+    }
+    int a, b, c, d;
+    edge_vertices<DIM>(i - NV, a, b);
+    edge_vertices<DIM>(j - NV, c, d);
+    return 0.25 * (gg(a, c) * m2(b, d) + gg(a, d) * m2(b, c) + gg(b, c) * m2(a, d) + gg(b, d) * m2(a, c));
+  }
+};
+
+template <int DIM, int ORDER>
+__global__ void __launch_bounds__(XMT) k_xfem_mom(ngsx_mesh M, const double *__restrict__ lset, const CutTable *__restrict__ tab, int dt,
+                                                 const double4 *__restrict__ rule_vol, int nr_vol, const double4 *__restrict__ rule_if, int nr_if,
+                                                 XTermsDev X, int64_t nlist, const int32_t *__restrict__ els, const int8_t *__restrict__ xsign,
+                                                 const double *__restrict__ ratio, int accumulate, double *__restrict__ mats) {
+  using XM = XMom<DIM, ORDER>;
+  constexpr int ND = XM::ND, NV = XM::NV, NEDGE = XM::NEDGE, N2C = 2 * ND;
   extern __shared__ __align__(16) unsigned char xsmem[];
-  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  // per warp: stage [XQ][ND] x (value, dn, gx, gy, gz) + weights [XQ] + base matrices [4][NE] + term coefficients
-  double *wbase = reinterpret_cast<double *>(xsmem) + warp * (XQ * ND * 5 + XQ + 4 * NE + XMAXTERMS);
-  double *stage = wbase, *facq = wbase + XQ * ND * 5, *base = facq + XQ, *tc = base + 4 * NE;
-  const bool need_k = [&] { bool b = false; for (int t = 0; t < X.n; t++) b |= X.pair[t] == 4; return b; }();
-  const bool need_b = [&] { bool b = false; for (int t = 0; t < X.n; t++) b |= X.pair[t] != 4; return b; }();
-  const int64_t nwarps = (int64_t)gridDim.x * XW;
-  for (int64_t k = (int64_t)blockIdx.x * XW + warp; k < nlist; k += nwarps) {
+  double4 *srule = reinterpret_cast<double4 *>(xsmem);                  // volume rule, then interface rule
+  CutEntry *lut = reinterpret_cast<CutEntry *>(srule + nr_vol + nr_if);
+  double *coefs = reinterpret_cast<double *>(lut + 16) + threadIdx.x * XCO;
+  double *wmem = reinterpret_cast<double *>(lut + 16) + XMT * XCO + threadIdx.x * XM::TOT;
+  for (int i = threadIdx.x; i < nr_vol; i += blockDim.x) srule[i] = rule_vol[i];
+  for (int i = threadIdx.x; i < nr_if; i += blockDim.x) srule[nr_vol + i] = rule_if[i];
+  if (threadIdx.x < 16) lut[threadIdx.x] = tab->e[DIM - 2][dt][threadIdx.x];
+  __syncthreads();
+  bool use0 = false, use1 = false, use2 = false, use3 = false, use4 = false;
+  for (int t = 0; t < X.n; t++) {
+    const int pr = X.pair[t];
+    use0 |= pr == 0; use1 |= pr == 1; use2 |= pr == 2; use3 |= pr == 3; use4 |= pr == 4;
+  }
+  const bool IFACE = dt == IF;
+  for (int64_t k = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; k < nlist; k += (int64_t)gridDim.x * blockDim.x) {
     const int64_t e = els ? els[k] : k;
     double ls[4], p[DIM + 1][DIM];
     xload_el<DIM>(M, lset, e, ls, p);
     int mask;
     const int dom = sign_test<DIM>(ls, mask);
     const bool cut = dom == IF;
-    double aM[T], aN[T], aD[T], aK[T];
+    double meas;
+    {
+      double m0 = 0.0, m1[NV], m2[XM::N2], mT[NV][XM::NT], mQ[XM::NQ];
 #pragma unroll
-    for (int t = 0; t < T; t++) aM[t] = aN[t] = aD[t] = aK[t] = 0.0;
-    ElGeom<DIM> G;
-    element_geometry<DIM>(p, G);
-    const double meas = fabs(G.det);
-    if (cut || dom == dt) {
+      for (int a = 0; a < NV; a++) {
+        m1[a] = 0.0;
+#pragma unroll
+        for (int t = 0; t < XM::NT; t++) mT[a][t] = 0.0;
+      }
+#pragma unroll
+      for (int t = 0; t < XM::N2; t++) m2[t] = 0.0;
+#pragma unroll
+      for (int t = 0; t < XM::NQ; t++) mQ[t] = 0.0;
+      ElGeom<DIM> G;
+      element_geometry<DIM>(p, G);
+      meas = fabs(G.det);
       double gl[DIM + 1][DIM];
 #pragma unroll
       for (int d = 0; d < DIM; d++) {
@@ -96,107 +194,154 @@ __global__ void __launch_bounds__(XW * 32) k_xfem(ngsx_mesh M, const double *__r
         const double inv = 1.0 / sqrt(g2);
 #pragma unroll
         for (int d = 0; d < DIM; d++) nrm[d] *= inv;
-        if (cut && dt == IF) scale = sqrt(g2) / sqrt(r2);               // |F^-T n_ref| (straightcutrule.cpp:558-576)
+        if (cut && IFACE) scale = sqrt(g2) / sqrt(r2);                  // |F^-T n_ref| (straightcutrule.cpp:558-576)
       }
-      CutEntry E;
-      if (cut) E = tab->e[DIM - 2][dt][mask]; else { E.ns = 1; E.npt = 0; }
-      const double4 *rule = (cut && dt == IF) ? rule_if : rule_vol;
-      const int nr = (cut && dt == IF) ? nr_if : nr_vol;
-      for (int s = 0; s < E.ns; s++) {
-        double P[4][3];
-        double sfac = 1.0;
-        if (cut) {
-          for (int v = 0; v < E.npt; v++) coded_point<DIM>(E.v[s][v], ls, P[v]);
-          sfac = simplex_factor(E.npt, P);
+      // geometry part of the slice: g_a = grad lam_a . n and the Gram matrix of the barycentric gradients
+#pragma unroll
+      for (int a = 0; a < NV; a++) {
+        double v = 0.0;
+#pragma unroll
+        for (int d = 0; d < DIM; d++) v = fma(gl[a][d], nrm[d], v);
+        wmem[XM::O_G + a] = v;
+#pragma unroll
+        for (int b = 0; b <= a; b++) {
+          double w = 0.0;
+#pragma unroll
+          for (int d = 0; d < DIM; d++) w = fma(gl[a][d], gl[b][d], w);
+          wmem[XM::O_GM + a * (a + 1) / 2 + b] = w;
         }
-        for (int q0 = 0; q0 < nr; q0 += XQ) {
-          const int nq = min(XQ, nr - q0);
-          if (lane < nq) {
-            const double4 r = rule[q0 + lane];
+      }
+      if (cut || dom == dt) {
+        CutEntry E;
+        if (cut) E = lut[mask]; else { E.ns = 1; E.npt = 0; }
+        const double4 *rule = (cut && IFACE) ? srule + nr_vol : srule;
+        const int nr = (cut && IFACE) ? nr_if : nr_vol;
+        for (int sub = 0; sub < E.ns; sub++) {
+          double P[4][3];
+          double sfac = 1.0;
+          if (cut) {
+            if (IFACE) {
+#pragma unroll
+              for (int v = 0; v < DIM; v++) coded_point<DIM>(E.v[sub][v], ls, P[v]);
+              sfac = simplex_factor(DIM, P);
+            } else {
+#pragma unroll
+              for (int v = 0; v <= DIM; v++) coded_point<DIM>(E.v[sub][v], ls, P[v]);
+              sfac = simplex_factor(DIM + 1, P);
+            }
+          }
+          const double f0 = meas * sfac * scale;
+          for (int q = 0; q < nr; q++) {
+            const double4 r = rule[q];
             double xi[3] = {r.x, r.y, r.z};
-            if (cut) simplex_point(E.npt, P, r, xi);
-            double lam[4] = {xi[0], xi[1], xi[2], 0.0};
+            if (cut) { if (IFACE) simplex_point(DIM, P, r, xi); else simplex_point(DIM + 1, P, r, xi); }
+            double lam[NV], fl[NV];
             double last = 1.0;
 #pragma unroll
-            for (int kk = 0; kk < DIM; kk++) last -= lam[kk];
+            for (int kk = 0; kk < DIM; kk++) { lam[kk] = xi[kk]; last -= xi[kk]; }
             lam[DIM] = last;
+            const double f = f0 * r.w;
+            m0 += f;
 #pragma unroll
-            for (int i = 0; i < ND; i++) {
-              double sv, gv[DIM];
-              h1_shape_grad<DIM, ORDER>(i, lam, gl, sv, gv);
-              double dn = 0.0;
+            for (int a = 0; a < NV; a++) {
+              fl[a] = f * lam[a];
+              m1[a] += fl[a];
 #pragma unroll
-              for (int d = 0; d < DIM; d++) dn += gv[d] * nrm[d];
-              double *o = stage + (lane * ND + i) * 5;
-              o[0] = sv; o[1] = dn; o[2] = gv[0]; o[3] = gv[1]; o[4] = DIM == 3 ? gv[DIM - 1] : 0.0;
+              for (int b = 0; b <= a; b++) m2[a * (a + 1) / 2 + b] = fma(fl[a], lam[b], m2[a * (a + 1) / 2 + b]);
             }
-            facq[lane] = meas * (r.w * sfac * scale);
-          }
-          __syncwarp();
-          for (int q = 0; q < nq; q++) {
-            const double f = facq[q];
+            if constexpr (ORDER == 2) {
+              double ep[XM::NT];
 #pragma unroll
-            for (int t = 0; t < T; t++) {
-              const int idx = lane + 32 * t;
-              if (idx < NE) {
-                const double *bi = stage + (q * ND + idx / ND) * 5, *bj = stage + (q * ND + idx % ND) * 5;
-                if (need_b) {
-                  aM[t] += f * bi[0] * bj[0];
-                  aN[t] += f * bi[0] * bj[1];
-                  aD[t] += f * bi[1] * bj[1];
-                }
-                if (need_k) aK[t] += f * (bi[2] * bj[2] + bi[3] * bj[3] + bi[4] * bj[4]);
+              for (int ed = 0; ed < NEDGE; ed++) {
+                int a, b;
+                edge_vertices<DIM>(ed, a, b);
+                ep[ed] = lam[a] * lam[b];
+              }
+#pragma unroll
+              for (int a = 0; a < NV; a++)
+#pragma unroll
+                for (int ed = 0; ed < NEDGE; ed++) mT[a][ed] = fma(fl[a], ep[ed], mT[a][ed]);
+              int t = 0;
+#pragma unroll
+              for (int ed = 0; ed < NEDGE; ed++) {
+                const double fe = f * ep[ed];
+#pragma unroll
+                for (int e2 = 0; e2 <= ed; e2++) { mQ[t] = fma(fe, ep[e2], mQ[t]); t++; }
               }
             }
           }
-          __syncwarp();
         }
       }
-    }
+      wmem[0] = m0;
 #pragma unroll
-    for (int t = 0; t < T; t++) {
-      const int idx = lane + 32 * t;
-      if (idx < NE) { base[idx] = aM[t]; base[NE + idx] = aN[t]; base[2 * NE + idx] = aD[t]; base[3 * NE + idx] = aK[t]; }
-    }
-    if (lane < X.n) {
-      const double h = DIM == 2 ? sqrt(meas) : cbrt(meas);                // specialcf.mesh_size
-      const double kap = __ldg(ratio + e);                                // CutRatioGF (xfem/cutinfo.cpp:91)
-      const double kf = X.kappa[lane] == 0 ? 1.0 : (X.kappa[lane] == 1 ? kap : 1.0 - kap);
-      tc[lane] = X.coef[lane] * xipow(h, X.hpow[lane]) * kf;
-    }
-    __syncwarp();
-    // compound block: row I = test function, column J = trial function; index = block * ND + local dof
-    const int8_t *sg = xsign + k * ND;
-    double *out = mats + k * (N2 * N2);
-    for (int idx = lane; idx < N2 * N2; idx += 32) {
-      const int I = idx / N2, J = idx - I * N2;
-      const int bI = I >= ND, i = I - bI * ND, bJ = J >= ND, j = J - bJ * ND;
-      // blk 0: std dofs; blk 1 / 2: x dofs whose sign is NEG / POS
-      const int cI = bI ? 1 + (int)sg[i] : 0, cJ = bJ ? 1 + (int)sg[j] : 0;
-      double v = 0.0;
-      const int c = cI * 3 + cJ;
-      for (int t = X.cls[c]; t < X.cls[c + 1]; t++) {
-        const int pr = X.pair[t];
-        const double b = pr == 0 ? base[i * ND + j] : (pr == 1 ? base[NE + i * ND + j] : (pr == 2 ? base[NE + j * ND + i]
-                         : (pr == 3 ? base[2 * NE + i * ND + j] : base[3 * NE + i * ND + j])));
-        v += tc[t] * b;
+      for (int a = 0; a < NV; a++) {
+        wmem[XM::O_M1 + a] = m1[a];
+#pragma unroll
+        for (int t = 0; t < XM::NT; t++) wmem[XM::O_MT + a * XM::NT + t] = mT[a][t];
       }
-      out[idx] = v;
+#pragma unroll
+      for (int t = 0; t < XM::N2; t++) wmem[XM::O_M2 + t] = m2[t];
+#pragma unroll
+      for (int t = 0; t < XM::NQ; t++) wmem[XM::O_MQ + t] = mQ[t];
     }
-    __syncwarp();
+    // the form's terms, folded per block class (test block * 3 + trial block) and operator pair
+    {
+      const double h = DIM == 2 ? sqrt(meas) : cbrt(meas);              // specialcf.mesh_size
+      const double kap = __ldg(ratio + e);                              // CutRatioGF (xfem/cutinfo.cpp:91)
+      for (int c = 0; c < 9; c++) {
+        double acc[5] = {0.0, 0.0, 0.0, 0.0, 0.0};
+        for (int t = X.cls[c]; t < X.cls[c + 1]; t++) {
+          const double kf = X.kappa[t] == 0 ? 1.0 : (X.kappa[t] == 1 ? kap : 1.0 - kap);
+          const double v = X.coef[t] * xipow(h, X.hpow[t]) * kf;
+          const int pr = X.pair[t];
+#pragma unroll
+          for (int q = 0; q < 5; q++) acc[q] += pr == q ? v : 0.0;
+        }
+#pragma unroll
+        for (int q = 0; q < 5; q++) coefs[c * 5 + q] = acc[q];
+      }
+    }
+    const XM W{wmem};
+    const int8_t *sg = xsign + k * ND;
+    double *out = mats + k * (N2C * N2C);
+#pragma unroll 1
+    for (int i = 0; i < ND; i++) {
+      const int ci = 1 + (int)__ldg(sg + i);                            // block class of the x copy of dof i (1 + its sign)
+#pragma unroll 1
+      for (int j = 0; j < ND; j++) {
+        const int cj = 1 + (int)__ldg(sg + j);
+        // operator pairs (test, trial): 0 val-val, 1 val-dn, 2 dn-val, 3 dn-dn, 4 grad.grad
+        const double b0 = use0 ? W.M(i, j) : 0.0, b1 = use1 ? W.N(i, j) : 0.0, b2 = use2 ? W.N(j, i) : 0.0;
+        const double b3 = use3 ? W.D(i, j) : 0.0, b4 = use4 ? W.K(i, j) : 0.0;
+#pragma unroll
+        for (int bI = 0; bI < 2; bI++)
+#pragma unroll
+          for (int bJ = 0; bJ < 2; bJ++) {
+            const int c = (bI ? ci : 0) * 3 + (bJ ? cj : 0);
+            const double *cf = coefs + c * 5;
+            double v = cf[0] * b0;
+            v = fma(cf[1], b1, v); v = fma(cf[2], b2, v); v = fma(cf[3], b3, v); v = fma(cf[4], b4, v);
+            double *o = out + (bI * ND + i) * N2C + bJ * ND + j;
+            *o = accumulate ? *o + v : v;
+          }
+      }
+    }
   }
 }
 
 template <int DIM, int ORDER>
 static int launch_xfem(const ngsx_mesh &M, const double *lset, const DeviceData *dd, int dt, const double4 *rv, int nv, const double4 *ri, int ni,
-                       const XTermsDev &X, int64_t nlist, const int32_t *els, const int8_t *xsign, const double *ratio, double *mats, cudaStream_t st) {
-  constexpr int ND = H1<DIM, ORDER>::ND, NE = ND * ND;
-  const size_t smem = (size_t)XW * (XQ * ND * 5 + XQ + 4 * NE + XMAXTERMS) * sizeof(double);
-  auto kern = k_xfem<DIM, ORDER>;
+                       const XTermsDev &X, int64_t nlist, const int32_t *els, const int8_t *xsign, const double *ratio, int accumulate, double *mats,
+                       cudaStream_t st) {
+  const size_t smem = (size_t)(nv + ni) * sizeof(double4) + 16 * sizeof(CutEntry) + (size_t)XMT * (XCO + XMom<DIM, ORDER>::TOT) * sizeof(double);
+  auto kern = k_xfem_mom<DIM, ORDER>;
   NGSX_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-  const int64_t need = (nlist + XW - 1) / XW;
-  const unsigned grid = (unsigned)std::max<int64_t>(1, std::min<int64_t>(need, (int64_t)dd->sm_count * 8));
-  kern<<<grid, XW * 32, smem, st>>>(M, lset, dd->cut_table, dt, rv, nv, ri, ni, X, nlist, els, xsign, ratio, mats);
+  int occ = 0;
+  NGSX_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, kern, XMT, smem));
+  if (occ < 1) { set_error("xfem_elmat: kernel does not fit on an SM"); return NGSX_ERR_CUDA; }
+  const int64_t need = (nlist + XMT - 1) / XMT;
+  const unsigned grid = (unsigned)std::max<int64_t>(1, std::min<int64_t>(need, (int64_t)dd->sm_count * occ));
+  kern<<<grid, XMT, smem, st>>>(M, lset, dd->cut_table, dt, rv, nv, ri, ni, X, nlist, els, xsign, ratio, accumulate, mats);
   NGSX_LAUNCH_CHECK();
   return NGSX_OK;
 }
@@ -207,7 +352,7 @@ using namespace ngsx;
 
 extern "C" int ngsx_xfem_elmat_h1(const ngsx_mesh *mesh, const double *lset_v, int fe_order, int dt, int intorder, int32_t nterms,
                                   const ngsx_xterm *h_terms, int64_t nlist, const int32_t *els, const int8_t *xsign, const double *ratio,
-                                  double *mats, void *stream) {
+                                  int accumulate, double *mats, void *stream) {
   NGSX_REQUIRE(mesh && (mesh->dim == 2 || mesh->dim == 3) && mesh->vert && mesh->el2v && lset_v, "xfem_elmat: bad mesh / level set");
   NGSX_REQUIRE(dt >= 0 && dt <= 2 && nlist >= 0 && nterms >= 0 && (nterms == 0 || h_terms), "xfem_elmat: bad arguments");
   NGSX_REQUIRE(nlist == 0 || (xsign && ratio && mats), "xfem_elmat: NULL array");
@@ -246,10 +391,10 @@ extern "C" int ngsx_xfem_elmat_h1(const ngsx_mesh *mesh, const double *lset_v, i
   if (nlist == 0) return NGSX_OK;
   cudaStream_t st = as_stream(stream);
   switch (mesh->dim * 10 + fe_order) {
-    case 21: return launch_xfem<2, 1>(*mesh, lset_v, dd, dt, rv, nv, ri, ni, X, nlist, els, xsign, ratio, mats, st);
-    case 22: return launch_xfem<2, 2>(*mesh, lset_v, dd, dt, rv, nv, ri, ni, X, nlist, els, xsign, ratio, mats, st);
-    case 31: return launch_xfem<3, 1>(*mesh, lset_v, dd, dt, rv, nv, ri, ni, X, nlist, els, xsign, ratio, mats, st);
-    case 32: return launch_xfem<3, 2>(*mesh, lset_v, dd, dt, rv, nv, ri, ni, X, nlist, els, xsign, ratio, mats, st);
+    case 21: return launch_xfem<2, 1>(*mesh, lset_v, dd, dt, rv, nv, ri, ni, X, nlist, els, xsign, ratio, accumulate, mats, st);
+    case 22: return launch_xfem<2, 2>(*mesh, lset_v, dd, dt, rv, nv, ri, ni, X, nlist, els, xsign, ratio, accumulate, mats, st);
+    case 31: return launch_xfem<3, 1>(*mesh, lset_v, dd, dt, rv, nv, ri, ni, X, nlist, els, xsign, ratio, accumulate, mats, st);
+    case 32: return launch_xfem<3, 2>(*mesh, lset_v, dd, dt, rv, nv, ri, ni, X, nlist, els, xsign, ratio, accumulate, mats, st);
   }
   return NGSX_ERR_UNSUPPORTED;
 }

@@ -404,6 +404,15 @@ def color_list(table: torch.Tensor, ndof: int, group: int):
     return perm.to(table.device), cptr[: nc.value + 1].tolist()
 
 
+
+class _XPlan:
+    """compound integrator: its product terms, the row plan of its Vh part on the uncut elements, and the gather plan + block
+    buffer over [dofs of Vh | x-dofs] of the IF elements that all compound integrators of the form share"""
+
+    def __init__(self, shared, xterms, plan_a):
+        self.shared, self.xterms, self.plan_a = shared, xterms, plan_a
+        self.els, self.handle, self.mats = shared.els, shared.handle, shared.mats
+
 class BilinearForm:
     """T_BilinearForm<double> stand-in: `a += integrator`, `a.Assemble()`, `a.mat` (CSR on the device).
     The sparsity is the full element (and, with dgjumps, facet-patch) graph like NGSolve's GetGraph."""
@@ -415,6 +424,7 @@ class BilinearForm:
         self.integrators: List = []
         self.mat: Optional[CSRMatrix] = None
         self._plans: Dict[int, _Plan] = {}
+        self._xshared = None
         self._graph_key = None
         self._err = torch.zeros((1, 2), dtype=torch.int64, device=space.mesh.device)     # one {count, first} per integrator
         self._err_armed = False
@@ -505,18 +515,19 @@ class BilinearForm:
         if self._h1 is fes:
             raise NgsxError(-1, "neg / pos operators need a BilinearForm on FESpace([Vh, XFESpace(Vh)])")
         plan_a = self._row_plan(integ) if (integ.dt != IF and integ.has_std) else None
-        ctab = fes.compound_table()
-        h = ctypes.c_void_p()
-        lo, hi = self.row_range if self.row_range is not None else (0, fes.ndof)
-        check(L.ngsx_rowplan_create(ctab.shape[0], ctab.shape[1], _ptr(ctab), fes.ndof, _ptr(self.mat.rowptr), _ptr(self.mat.colidx),
-                                    lo, hi, ctypes.byref(h), _stream()))
-        info = (ctypes.c_int64 * 6)()
-        check(L.ngsx_rowplan_info(h, info))
-        plan_b = _RowPlan(fes.x.if_els, ctab, h, tuple(info))
-        plan_b.mats = torch.empty((ctab.shape[0], ctab.shape[1] ** 2), dtype=torch.float64, device=fes.mesh.device)
+        if self._xshared is None:                                  # one gather plan + one block buffer for all compound integrators
+            ctab = fes.compound_table()
+            h = ctypes.c_void_p()
+            lo, hi = self.row_range if self.row_range is not None else (0, fes.ndof)
+            check(L.ngsx_rowplan_create(ctab.shape[0], ctab.shape[1], _ptr(ctab), fes.ndof, _ptr(self.mat.rowptr), _ptr(self.mat.colidx),
+                                        lo, hi, ctypes.byref(h), _stream()))
+            info = (ctypes.c_int64 * 6)()
+            check(L.ngsx_rowplan_info(h, info))
+            shared = _RowPlan(fes.x.if_els, ctab, h, tuple(info))
+            shared.mats = torch.empty((ctab.shape[0], ctab.shape[1] ** 2), dtype=torch.float64, device=fes.mesh.device)
+            self._xshared = shared
         from . import xfes
-        plan_b.xterms = xfes.make_xterms(integ.xterms)
-        plan_b.plan_a = plan_a
+        plan_b = _XPlan(self._xshared, xfes.make_xterms(integ.xterms), plan_a)
         return plan_b
 
     def _row_plan(self, integ: SymbolicCutBFI) -> _RowPlan:
@@ -601,6 +612,7 @@ class BilinearForm:
         if self.mat is None or reallocate:
             self._build_graph()
             self._plans.clear()
+            self._xshared = None
         plans = [self._plan_for(k, integ) for k, integ in enumerate(self.integrators)]
         # a single row plan that covers every stored entry overwrites its rows: no SetZero pass, each value written once
         # (with a row range: the rank's rows are one contiguous CSR span, the other rows belong to other ranks and stay untouched)
@@ -613,12 +625,13 @@ class BilinearForm:
         if self._err.shape[0] < len(plans):
             self._err = torch.zeros((len(plans), 2), dtype=torch.int64, device=fes.mesh.device)
         mesh_c = ctypes.byref(fes.mesh.c_struct())
+        x_blocks = 0                                               # compound integrators whose IF blocks sit in the shared buffer
         for k, integ in enumerate(self.integrators):
             plan = plans[k]
             if isinstance(integ, SymbolicFacetPatchBFI):
                 self._assemble_facetpatch(integ, plan)
             elif integ.xterms is not None:
-                self._assemble_x(integ, plan, k)
+                x_blocks += self._assemble_x(integ, plan, k, x_blocks)
             elif isinstance(plan, _RowPlan):
                 lv = _lset_vec(integ.lset)
                 check(L.ngsx_assemble_csr_rows_h1(mesh_c, _ptr(lv), fes.order, integ.dt, integ.intorder(fes.order), ctypes.byref(integ.form),
@@ -630,6 +643,8 @@ class BilinearForm:
                 check(L.ngsx_assemble_csr_h1(mesh_c, _ptr(lv), fes.order, integ.dt, integ.intorder(fes.order), ctypes.byref(integ.form),
                                              plan.els.numel(), _ptr(plan.els), _ptr(plan.slots), plan.ncolors, plan.h_color_ptr,
                                              plan.group, _ptr(self.mat.vals), _stream()))
+        if x_blocks:                                               # one gather for the summed blocks of all compound integrators
+            check(L.ngsx_assemble_csr_rows_mats(self._xshared.handle, _ptr(self._xshared.mats), 1, _ptr(self.mat.vals), _stream()))
         return self
 
     def check_degenerate(self, err=None):
@@ -653,9 +668,9 @@ class BilinearForm:
         self._err_armed = False
         return self._err
 
-    def _assemble_x(self, integ, plan, k):
-        """compound integrator: Vh part on the uncut elements through the H1 row gather, then the (2 nd)^2 blocks of the IF elements
-        (ngsx_xfem_elmat_h1) through the matrix-fed gather; both add in plan order"""
+    def _assemble_x(self, integ, plan, k, x_blocks):
+        """compound integrator: Vh part on the uncut elements through the H1 row gather; the (2 nd)^2 blocks of the IF elements
+        (ngsx_xfem_elmat_h1) are summed over the form's compound integrators in one buffer that Assemble gathers once"""
         L = _lib_()
         fes, h1 = self.space, self._h1
         lv = _lset_vec(integ.lset)
@@ -669,8 +684,9 @@ class BilinearForm:
         n = plan.els.numel()
         if n:
             check(L.ngsx_xfem_elmat_h1(mesh_c, _ptr(lv), h1.order, integ.dt, io, len(integ.xterms), plan.xterms, n, _ptr(plan.els),
-                                       _ptr(fes.x.xsign), _ptr(fes.x.cutinfo.ratio), _ptr(plan.mats), _stream()))
-            check(L.ngsx_assemble_csr_rows_mats(plan.handle, _ptr(plan.mats), 1, _ptr(self.mat.vals), _stream()))
+                                       _ptr(fes.x.xsign), _ptr(fes.x.cutinfo.ratio), 1 if x_blocks else 0, _ptr(plan.mats), _stream()))
+            return 1
+        return 0
 
     def _assemble_facetpatch(self, integ, plan):
         """numeric phase: merged patch blocks (ngsx_facetpatch_cmat_h1), then the owner-computes gather adds them to the rows
