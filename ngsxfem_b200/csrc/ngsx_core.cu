@@ -282,7 +282,7 @@ __global__ void __launch_bounds__(STREAM_THREADS, NGSX_CLS_MINB) k_classify(ngsx
                                                                double *__restrict__ ratio, unsigned long long *__restrict__ err) {
   extern __shared__ __align__(128) unsigned char smem_stream[];
   stream_elements<DIM>(M, smem_stream, [&](int64_t c, int64_t first, int n, const int32_t *stage, int nstaged) {
-    if (n == STREAM_CH) classify_chunk<DIM, true>(M, lset, words, ifwords, nwords, dom_out, ratio, err, c, first, n, stage, nstaged);
+    if (n == STREAM_CH && nstaged == STREAM_CH) classify_chunk<DIM, true>(M, lset, words, ifwords, nwords, dom_out, ratio, err, c, first, n, stage, nstaged);
     else classify_chunk<DIM, false>(M, lset, words, ifwords, nwords, dom_out, ratio, err, c, first, n, stage, nstaged);
   });
 }
@@ -557,7 +557,7 @@ __global__ void __launch_bounds__(STREAM_THREADS, NGSX_INT_MINB) k_int_uncut(ngs
                                                                 uint32_t *__restrict__ cutwords, int64_t nred) {
   extern __shared__ __align__(128) unsigned char smem_stream[];
   stream_elements<DIM>(M, smem_stream, [&](int64_t c, int64_t first, int n, const int32_t *stage, int nstaged) {
-    if (n == STREAM_CH) int_uncut_chunk<DIM, true>(M, lset, dt, rule_vol, nr_vol, f, fconst, wref_vol, partial, cutwords, nred, c, first, n, stage, nstaged);
+    if (n == STREAM_CH && nstaged == STREAM_CH) int_uncut_chunk<DIM, true>(M, lset, dt, rule_vol, nr_vol, f, fconst, wref_vol, partial, cutwords, nred, c, first, n, stage, nstaged);
     else int_uncut_chunk<DIM, false>(M, lset, dt, rule_vol, nr_vol, f, fconst, wref_vol, partial, cutwords, nred, c, first, n, stage, nstaged);
   });
   // words beyond the last chunk (the reduction length is padded to a multiple of 8 words)
@@ -787,7 +787,7 @@ int ngsx_classify(const ngsx_mesh *mesh, const double *lset_v, uint32_t *cdom_wo
   if (mesh->ne == 0) return NGSX_OK;
   int64_t nwords = (mesh->ne + 31) / 32;
   auto *e = reinterpret_cast<unsigned long long *>(err);
-  NGSX_REQUIRE((reinterpret_cast<uintptr_t>(mesh->el2v) & 15u) == 0, "classify: mesh.el2v must be 16-byte aligned");
+  NGSX_REQUIRE(mesh->dim == 2 || (reinterpret_cast<uintptr_t>(mesh->el2v) & 15u) == 0, "classify: a 3D mesh.el2v must be 16-byte aligned");
   uint32_t *ifwords = cdom_words ? cdom_words + NGSX_CDOM_IF * nwords : nullptr, *tmp = nullptr;
   if (ratio && !ifwords) {
     NGSX_CUDA(cudaMallocAsync(&tmp, nwords * sizeof(uint32_t), st));
@@ -915,7 +915,7 @@ int ngsx_integrate(const ngsx_mesh *mesh, const double *lset_v, int dt, int orde
   uint32_t *cutwords = nullptr;
   NGSX_CUDA(cudaMallocAsync(&partial, (nred + nmid) * sizeof(double), st));
   NGSX_CUDA(cudaMallocAsync(&cutwords, nred * sizeof(uint32_t), st));
-  NGSX_REQUIRE((reinterpret_cast<uintptr_t>(mesh->el2v) & 15u) == 0, "integrate: mesh.el2v must be 16-byte aligned");
+  NGSX_REQUIRE(mesh->dim == 2 || (reinterpret_cast<uintptr_t>(mesh->el2v) & 15u) == 0, "integrate: a 3D mesh.el2v must be 16-byte aligned");
   const int64_t nchunks = (ne + STREAM_CH - 1) / STREAM_CH;
   const unsigned nb = (unsigned)std::min<int64_t>(nchunks, (int64_t)dd->sm_count * NGSX_INT_MINB);   // persistent
   const unsigned ncut = (unsigned)(((nred + 31) / 32 + CUT_G - 1) / CUT_G);                    // one CTA per CUT_G chunks of 32 words

@@ -69,10 +69,12 @@ __device__ __forceinline__ void stream_elements(const ngsx_mesh &M, unsigned cha
   const uint32_t s_bar = s_base + STREAM_NST * STAGE;
   const int64_t nchunks = (M.ne + STREAM_CH - 1) / STREAM_CH;
   const unsigned char *g = reinterpret_cast<const unsigned char *>(M.el2v);
+  // a 2D table that does not start on a 16-byte boundary (element blocks of a partition) is read directly, nothing is staged
+  const uint32_t granule = (reinterpret_cast<uintptr_t>(g) & 15u) == 0 ? ~15u : 0u;
   auto issue = [&](int64_t c, int st) {
     const int64_t first = c * STREAM_CH;
     const int64_t n = M.ne - first < STREAM_CH ? M.ne - first : STREAM_CH;
-    const uint32_t bytes = (uint32_t)(n * ELB) & ~15u;
+    const uint32_t bytes = (uint32_t)(n * ELB) & granule;
     if (bytes) {
       mbar_expect_tx(s_bar + 8 * st, bytes);
       bulk_g2s(s_base + st * STAGE, g + first * ELB, bytes, s_bar + 8 * st);
@@ -97,7 +99,7 @@ __device__ __forceinline__ void stream_elements(const ngsx_mesh &M, unsigned cha
     mbar_wait(s_bar + 8 * st, (uint32_t)(it / STREAM_NST) & 1u);
     const int64_t first = c * STREAM_CH;
     const int n = (int)(M.ne - first < STREAM_CH ? M.ne - first : STREAM_CH);
-    body(c, first, n, reinterpret_cast<const int32_t *>(smem + (size_t)st * STAGE), (int)(((uint32_t)(n * ELB) & ~15u) / ELB));
+    body(c, first, n, reinterpret_cast<const int32_t *>(smem + (size_t)st * STAGE), (int)(((uint32_t)(n * ELB) & granule) / ELB));
     __syncthreads();                                  // every thread is done with the stage: refill it
     if (threadIdx.x == 0) {
       const int64_t c2 = c + (int64_t)STREAM_NST * gridDim.x;
