@@ -164,13 +164,16 @@ def run_b200(args):
     ev = lambda: torch.cuda.Event(enable_timing=True)
     stage_ms = {"classify": [], "assemble": [], "integrate": []}
 
-    # classification, assembly and the two Integrate() calls depend on the level set only: issued on four streams, the
-    # latency-bound sweeps and cut passes overlap the assembly chain (N = 1: 1.33 -> 1.22 ms).  At N > 1 every kernel is short
-    # and the extra stream bookkeeping on the host costs more than the overlap gains (measured at N = 4: 0.50 ms serial,
-    # 0.57 ms on four streams), so the ranks of a multi-GPU run keep one stream.
+    # classification and the two Integrate() calls depend on the level set only.  At N = 1 they are issued on three streams
+    # behind the assembly chain: the latency-bound sweeps and cut passes overlap each other (0.40 -> 0.34 ms), the row gather
+    # keeps the machine to itself (1.33 -> 1.25 ms per step).  Issued together with the assembly the step is 1.22 ms, but the
+    # row gather then shares its SMs (0.70 -> 0.79 ms) -- NGSX_BENCH_ORDER=with.  At N > 1 every kernel is short and the extra
+    # stream bookkeeping on the host costs more than the overlap gains (measured at N = 4: 0.50 ms serial, 0.57 ms on four
+    # streams), so the ranks of a multi-GPU run keep one stream.
     main = torch.cuda.current_stream()
     side = [torch.cuda.Stream() for _ in range(3)]
     serial = world > 1 or bool(os.environ.get("NGSX_BENCH_SERIAL"))      # NGSX_BENCH_SERIAL: A/B switch at N = 1
+    after_asm = os.environ.get("NGSX_BENCH_ORDER", "after") == "after"   # the three sweeps overlap each other, not the row gather
 
     def step(record, serial=serial):
         e = [ev() for _ in range(6)]
@@ -181,9 +184,9 @@ def run_b200(args):
             s_if = xfem.IntegrateX(lsetp1, mesh_int, cf=1.0, order=4, domain_type=xfem.IF, sync=False); e[3].record()
             s_neg = xfem.IntegrateX(lsetp1, mesh_int, cf=1.0, order=4, domain_type=xfem.NEG, sync=False); e[4].record()
         else:
-            a.Assemble(); e[2].record()                                  # the longest chain first, on the main stream
+            a.Assemble(); e[2].record()                                  # the assembly chain alone on the main stream
             for st in side:
-                st.wait_event(e[0])
+                st.wait_event(e[2] if after_asm else e[0])
             with torch.cuda.stream(side[0]):
                 ci.Update(lsetp1); e[1].record()
             with torch.cuda.stream(side[1]):
@@ -227,10 +230,11 @@ def run_b200(args):
     launches = L.ngsx_launch_count() - launches0
     L.ngsx_debug_set_timing(0)
     total_ms = t_begin.elapsed_time(t_end)
-    for e in rec:                                        # per stage: from the start of the step to the stage's last kernel, on its stream
-        stage_ms["classify"].append(e[0].elapsed_time(e[1]))
+    for e in rec:                                        # per stage: from its start event to its last kernel, on its stream
+        t0s = e[0] if (serial or not after_asm) else e[2]                    # the sweeps start when the assembly chain ends
+        stage_ms["classify"].append(e[0].elapsed_time(e[1]) if serial else t0s.elapsed_time(e[1]))
         stage_ms["assemble"].append(e[1].elapsed_time(e[2]) if serial else e[0].elapsed_time(e[2]))
-        stage_ms["integrate"].append(e[2].elapsed_time(e[4]) if serial else max(e[0].elapsed_time(e[3]), e[0].elapsed_time(e[4])))
+        stage_ms["integrate"].append(e[2].elapsed_time(e[4]) if serial else max(t0s.elapsed_time(e[3]), t0s.elapsed_time(e[4])))
 
     # stage / kernel breakdown without overlap: a few serial steps after the timed region (reported beside the overlapped figures)
     serial_break = None
@@ -365,7 +369,7 @@ def run_b200(args):
                    "ne": mesh.ne, "hasneg_elements": n_global, "nnz": nnz_global, "assembly": a.assembly, "group": args.group, "colors": plan.ncolors,
                    "setup_s_untimed": round(setup_s, 2), "stage_ms": {"classify": cl_ms, "assemble": as_ms, "integrate": in_ms},
                    "stage_ms_one_stream": serial_break,
-                   "streams": "1 (serial stages)" if serial else "4: assemble | CutInfo.Update | Integrate(IF) | Integrate(NEG) overlap; stage_ms = start of step to the stage's last kernel",
+                   "streams": "1 (serial stages)" if serial else "assemble, then CutInfo.Update | Integrate(IF) | Integrate(NEG) on three streams; stage_ms = stage start to its last kernel (the three sweeps overlap)",
                    "l2": "inputs larger than L2 (CSR values + pair descriptors + mesh > 1.4 GB touched per step vs 126 MB L2); no explicit flush",
                    "partition": "owner-computes: contiguous chunks of equal cost (cut element = 3.2 uncut) of the HASNEG element list per rank, a CSR row belongs to the rank of the first listed element touching it, halo elements re-evaluated, no interface-row exchange; element blocks for Integrate, scalars all-reduced (NCCL)"},
         "roofline": {"bound": "hbm", "kernel": "k_rows<10,6> (owner-computes row gather: every CSR value of the assembled operator written once)",

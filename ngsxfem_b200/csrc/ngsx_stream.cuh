@@ -16,7 +16,10 @@
 namespace ngsx {
 
 constexpr int STREAM_CH = 1024;      // elements per chunk
-constexpr int STREAM_NST = 4;        // chunks in flight per CTA
+#ifndef NGSX_STREAM_NST
+#define NGSX_STREAM_NST 4
+#endif
+constexpr int STREAM_NST = NGSX_STREAM_NST;   // chunks in flight per CTA
 constexpr int STREAM_THREADS = 256;  // 8 warps x 4 words x 32 lanes = one chunk
 constexpr int STREAM_WPW = 4;        // words per warp and chunk
 
