@@ -197,7 +197,14 @@ def IntegrateX(lset, mesh: Mesh, cf=None, order: int = 5, domain_type=IF, subdiv
 
 
 def Integrate(levelset_domain=None, cf=None, mesh=None, order=5, time_order=-1, heapsize=1000000, **kwargs):
-    """python/__init__.py:311-378: Integrate(levelset_domain={...}, cf=..., mesh=..., order=...)"""
+    """python/__init__.py:311-378: Integrate(levelset_domain={...}, cf=..., mesh=..., order=...); also Integrate(cf * dCut(...), mesh)"""
+    if isinstance(levelset_domain, CutIntegrand):
+        mesh = cf if (mesh is None and isinstance(cf, Mesh)) else mesh
+        total = 0.0
+        for f, sym in levelset_domain.parts:
+            ld = sym.levelset_domain
+            total += Integrate(levelset_domain=ld, cf=f, mesh=mesh, order=ld.get("force_intorder", order), time_order=time_order)
+        return total
     if levelset_domain is None or not isinstance(levelset_domain, dict):
         raise NgsxError(-2, "only Integrate(levelset_domain=...) is provided (plain NGSolve Integrate is not part of the path)")
     if mesh is None:
@@ -208,6 +215,55 @@ def Integrate(levelset_domain=None, cf=None, mesh=None, order=5, time_order=-1, 
     return IntegrateX(lset=ld["levelset"], mesh=mesh, cf=cf, order=order, domain_type=ld["domain_type"],
                       subdivlvl=ld.get("subdivlvl", 0), time_order=time_order,
                       quad_dir_policy=ld.get("quad_dir_policy", OPTIMAL), heapsize=heapsize)
+
+
+# ------------------------------------------------------------------------------------------------------------------
+# differential symbols: form * dCut(levelset, NEG) / form * dx(levelset_domain = {...}).  The reference at this revision only has
+# the SymbolicBFI(levelset_domain = ...) spelling (python/__init__.py:107-279); later ngsxfem releases and the task statement
+# name dCut / dx, so both spellings build the same integrators here.
+# ------------------------------------------------------------------------------------------------------------------
+class CutIntegrand:
+    """sum of (form, differential symbol) pairs: what `a += ...`, `f += ...` and Integrate(...) accept"""
+
+    def __init__(self, parts):
+        self.parts = list(parts)
+
+    def __add__(self, o):
+        return CutIntegrand(self.parts + o.parts) if isinstance(o, CutIntegrand) else NotImplemented
+
+
+class CutDifferentialSymbol:
+    def __init__(self, levelset_domain, definedonelements=None):
+        self.levelset_domain, self.definedonelements = dict(levelset_domain), definedonelements
+
+    def __call__(self, definedonelements=None, levelset_domain=None, **kwargs):
+        ld = dict(self.levelset_domain if levelset_domain is None else levelset_domain)
+        if "order" in kwargs and kwargs["order"] is not None:
+            ld["force_intorder"] = int(kwargs["order"])
+        return CutDifferentialSymbol(ld, self.definedonelements if definedonelements is None else definedonelements)
+
+    def __rmul__(self, form):
+        return CutIntegrand([(form, self)])
+
+
+def dCut(levelset, domain_type, order=None, subdivlvl=None, time_order=-1, levelset_domain=None, definedonelements=None, **kwargs):
+    """dCut(levelset, domain_type, order = None, ...): differential symbol of a cut integral (NEG / POS / IF part)"""
+    if time_order >= 0 or kwargs.get("deformation") is not None:
+        raise NgsxError(-2, "space-time / deformed dCut integrators are outside the CUDA path")
+    ld = dict(levelset_domain) if levelset_domain is not None else {}
+    ld.update({"levelset": levelset, "domain_type": domain_type})
+    if order is not None:
+        ld["force_intorder"] = int(order)
+    if subdivlvl:
+        ld["subdivlvl"] = subdivlvl
+    return CutDifferentialSymbol(ld, definedonelements)
+
+
+def dx(levelset_domain=None, definedonelements=None, **kwargs):
+    """dx(levelset_domain = {...}): the volume symbol restricted to a level-set domain (plain dx is NGSolve's, not part of the path)"""
+    if levelset_domain is None:
+        raise NgsxError(-2, "only dx(levelset_domain=...) is provided (uncut NGSolve integrators are not part of the path)")
+    return CutDifferentialSymbol(levelset_domain, definedonelements)
 
 
 # ------------------------------------------------------------------------------------------------------------------
@@ -433,6 +489,10 @@ class BilinearForm:
         self._h1 = getattr(space, "std", space)        # the H1 component (compound space [Vh, XFESpace]: its first component)
 
     def __iadd__(self, integ):
+        if isinstance(integ, CutIntegrand):                            # a += form * dCut(...) [+ form2 * dCut(...)]
+            for form, sym in integ.parts:
+                self += SymbolicBFI(levelset_domain=sym.levelset_domain, form=form, definedonelements=sym.definedonelements)
+            return self
         if not isinstance(integ, (SymbolicCutBFI, SymbolicFacetPatchBFI)):
             raise NgsxError(-2, "only SymbolicCutBFI / SymbolicFacetPatchBFI integrators are on the CUDA path")
         self.integrators.append(integ)
@@ -743,6 +803,10 @@ class LinearForm:
         self._xplans: Dict[int, tuple] = {}
 
     def __iadd__(self, integ):
+        if isinstance(integ, CutIntegrand):                            # f += form * dCut(...)
+            for form, sym in integ.parts:
+                self += SymbolicLFI(levelset_domain=sym.levelset_domain, form=form, definedonelements=sym.definedonelements)
+            return self
         if not isinstance(integ, SymbolicCutLFI):
             raise NgsxError(-2, "only SymbolicCutLFI integrators are on the CUDA path")
         if integ.has_x and not self.compound:

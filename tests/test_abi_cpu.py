@@ -172,3 +172,19 @@ def test_xfem_linearform_parse():
         xfem.SymbolicLFI(levelset_domain={"levelset": None, "domain_type": xfem.NEG}, form=Expr.atom("u") * v_std)
     with pytest.raises(NgsxError):
         xfem.SymbolicLFI(levelset_domain={"levelset": None, "domain_type": xfem.NEG}, form=ngs.specialcf.mesh_size * v_std)
+
+
+def test_dcut_symbols_build_the_same_integrators():
+    """form * dCut(lset, NEG, order=...) and form * dx(levelset_domain=...) are spellings of SymbolicBFI / SymbolicLFI(levelset_domain=...)"""
+    from ngsxfem_b200 import ngs, xfem
+    from ngsxfem_b200.ngs import Expr
+    u, v = Expr.atom("u"), Expr.atom("v")
+    form = ngs.grad_of(u) * ngs.grad_of(v) + u * v if hasattr(ngs, "grad_of") else u * v
+    integ = form * xfem.dCut(None, xfem.NEG, order=3)
+    assert isinstance(integ, xfem.CutIntegrand) and len(integ.parts) == 1
+    f, sym = integ.parts[0]
+    assert f is form and sym.levelset_domain == {"levelset": None, "domain_type": xfem.NEG, "force_intorder": 3}
+    two = form * xfem.dCut(None, xfem.NEG) + 2.0 * form * xfem.dx(levelset_domain={"levelset": None, "domain_type": xfem.POS})
+    assert [p[1].levelset_domain["domain_type"] for p in two.parts] == [xfem.NEG, xfem.POS]
+    rhs = (1.0 + ngs.x) * v * xfem.dCut(None, xfem.IF)
+    assert rhs.parts[0][0].poly.terms == {(0, 0, 0): 1.0, (1, 0, 0): 1.0}

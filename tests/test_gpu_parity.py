@@ -736,6 +736,33 @@ def test_streamed_sweeps_edge_sizes(X, dim):
                 assert abs(got - ref) <= 1e-12 * max(abs(ref), 1e-3), (lo, hi, dt)
 
 
+def test_dcut_spelling_matches_symbolic_bfi(X):
+    """a += form * dCut(lset, NEG), f += cf * v * dCut(...), Integrate(cf * dCut(...), mesh): same integrators, bitwise the same results
+    as the SymbolicBFI / SymbolicLFI / Integrate(levelset_domain=...) spelling of the reference (python/__init__.py:107-378)"""
+    xf, ngs = X.xfem, X.ngs
+    mesh = ngs.Mesh(X.meshes.MakeStructured3DMesh(7, device="cuda"))
+    gf = ngs.GridFunction(ngs.H1(mesh, order=1))
+    xf.InterpolateToP1(ngs.SphereLevelset((0.5, 0.5, 0.5), 0.33), gf)
+    Vh = ngs.H1(mesh, order=2)
+    u, v = Vh.TnT()
+    form = ngs.grad(u) * ngs.grad(v) + 0.5 * u * v
+    ld = {"levelset": gf, "domain_type": NEG}
+    a = xf.BilinearForm(Vh); a += xf.SymbolicBFI(levelset_domain=ld, form=form); a.Assemble()
+    b = xf.BilinearForm(Vh); b += form * xf.dCut(gf, NEG); b.Assemble()
+    c = xf.BilinearForm(Vh); c += form * xf.dx(levelset_domain=ld); c.Assemble()
+    assert torch.equal(a.mat.vals, b.mat.vals) and torch.equal(a.mat.vals, c.mat.vals) and a.mat.vals.abs().max() > 0
+    cf = 1.0 + ngs.x * ngs.y
+    f1 = xf.LinearForm(Vh); f1 += xf.SymbolicLFI(levelset_domain=ld, form=cf * v); f1.Assemble()
+    f2 = xf.LinearForm(Vh); f2 += cf * v * xf.dCut(gf, NEG); f2.Assemble()
+    assert torch.equal(f1.vec, f2.vec) and f1.vec.abs().max() > 0
+    i1 = xf.Integrate(levelset_domain={"levelset": gf, "domain_type": IF}, cf=cf, mesh=mesh, order=3)
+    i2 = xf.Integrate(cf * xf.dCut(gf, IF, order=3), mesh)
+    assert i1 == i2 and i1 > 0
+    both = xf.Integrate(cf * xf.dCut(gf, NEG, order=3) + cf * xf.dCut(gf, POS, order=3), mesh)
+    whole = 1.0 + 0.25
+    assert abs(both - whole) < 1e-12
+
+
 def test_unsupported_paths_raise(X):
     mesh = X.ngs.Mesh(X.meshes.MakeStructured2DMesh(2))
     gf = X.ngs.GridFunction(X.ngs.H1(mesh, order=1))
