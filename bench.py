@@ -175,8 +175,10 @@ def run_b200(args):
     serial = world > 1 or bool(os.environ.get("NGSX_BENCH_SERIAL"))      # NGSX_BENCH_SERIAL: A/B switch at N = 1
     after_asm = os.environ.get("NGSX_BENCH_ORDER", "after") == "after"   # the three sweeps overlap each other, not the row gather
 
-    def step(record, serial=serial):
-        e = [ev() for _ in range(6)]
+    def step(record, serial=serial, timing=True, order_after=after_asm):
+        mk = ev if timing else (lambda: torch.cuda.Event())              # no timing events inside a graph capture
+        e = [mk() for _ in range(6)]
+        cur = torch.cuda.current_stream()
         e[0].record()
         if serial:
             ci.Update(lsetp1); e[1].record()
@@ -186,7 +188,7 @@ def run_b200(args):
         else:
             a.Assemble(); e[2].record()                                  # the assembly chain alone on the main stream
             for st in side:
-                st.wait_event(e[2] if after_asm else e[0])
+                st.wait_event(e[2] if order_after else e[0])
             with torch.cuda.stream(side[0]):
                 ci.Update(lsetp1); e[1].record()
             with torch.cuda.stream(side[1]):
@@ -194,12 +196,44 @@ def run_b200(args):
             with torch.cuda.stream(side[2]):
                 s_neg = xfem.IntegrateX(lsetp1, mesh_int, cf=1.0, order=4, domain_type=xfem.NEG, sync=False); e[4].record()
             for st in side:
-                main.wait_stream(st)
-            s_if.record_stream(main); s_neg.record_stream(main)
+                cur.wait_stream(st)
+            s_if.record_stream(cur); s_neg.record_stream(cur)
         e[5].record()
         if record is not None:
             record.append(e)
         return s_if, s_neg
+
+    # N > 1: every kernel of a rank is short (1/N of the mesh), so launch gaps and the host-side stream bookkeeping decide the
+    # step.  The rank captures its step -- assembly chain and the three sweeps on forked streams -- into one CUDA graph and
+    # replays it; only the NCCL all-reduce of the two scalars stays outside.  (N = 1 stays eager: its kernels are long enough,
+    # and the library's per-kernel timing events for the roofline cannot be recorded inside a graph.)
+    graph, g_out, graph_note = None, None, "eager"
+    comm = torch.cuda.Stream() if (world > 1 and not os.environ.get("NGSX_BENCH_NOCOMMSTREAM")) else None
+    if world > 1 and not os.environ.get("NGSX_BENCH_NOGRAPH"):
+        try:
+            ref_if, ref_neg = step(None)
+            ref_vals = a.mat.vals.clone()
+            torch.cuda.synchronize()
+            graph = torch.cuda.CUDAGraph()
+            lps0 = L.ngsx_launch_count()
+            with torch.cuda.graph(graph):
+                g_out = step(None, serial=False, timing=False, order_after=os.environ.get("NGSX_BENCH_ORDER", "with") == "after")
+            launches_per_replay = L.ngsx_launch_count() - lps0           # kernel nodes of this library in the graph
+            a.mat.vals.fill_(float("nan"))
+            graph.replay()
+            torch.cuda.synchronize()
+            wrote = ~torch.isnan(a.mat.vals)                            # a rank writes the rows it owns, nothing else
+            chk = (int(wrote.sum()) >= plan.nnz_covered, torch.equal(a.mat.vals[wrote], ref_vals[wrote]),    # tiles also zero the empty rows they span
+                   torch.equal(g_out[0], ref_if), torch.equal(g_out[1], ref_neg))
+            if not all(chk):
+                raise RuntimeError(f"graph replay differs from the eager step {chk} {int(wrote.sum())} {plan.nnz_covered}")
+            a.mat.vals.copy_(ref_vals)
+            del wrote
+            graph_note = "CUDA graph per rank (assembly chain + three forked sweep streams), NCCL all-reduce outside"
+            del ref_vals
+        except Exception as exc:                                         # capture unsupported on this driver: stay eager
+            graph, graph_note = None, f"eager (graph capture failed: {type(exc).__name__}: {str(exc)[:200]})"
+            torch.cuda.synchronize()
 
     def barrier():
         if world > 1:
@@ -207,7 +241,10 @@ def run_b200(args):
         torch.cuda.synchronize()
 
     for _ in range(args.warmup):
-        step(None)
+        if graph is not None:
+            graph.replay()
+        else:
+            step(None)
     barrier()
     sampler = ClockSampler(lrank)
     sampler.start()
@@ -219,15 +256,32 @@ def run_b200(args):
     t_begin, t_end = ev(), ev()
     t_begin.record()
     for _ in range(args.steps):
-        s_if, s_neg = step(rec)
+        if graph is not None:
+            graph.replay()
+            s_if, s_neg = g_out
+        else:
+            s_if, s_neg = step(rec)
         if world > 1:                                    # the path's only exchange at this tier: scalar Integrate() all-reduce
-            sc = torch.cat([s_if, s_neg])
-            dist.all_reduce(sc)
+            sc = torch.cat([s_if, s_neg])                # (copies the two scalars out of the graph's static buffers)
+            if comm is None:
+                dist.all_reduce(sc)
+            else:                                        # on its own stream: the 16-byte exchange overlaps the next step's kernels
+                comm.wait_stream(main)
+                with torch.cuda.stream(comm):
+                    dist.all_reduce(sc)
+                sc.record_stream(comm)
+    if comm is not None:
+        main.wait_stream(comm)
     t_end.record()
     barrier()
+    launches = launches_per_replay * args.steps if graph is not None else L.ngsx_launch_count() - launches0
+    if graph is not None:                                # per-stage / per-kernel times of a graph run: eager serial steps after the timed region
+        L.ngsx_debug_set_timing(1)
+        for _ in range(5):
+            step(rec, serial=True)
+        torch.cuda.synchronize()
     if a.assembly == "rows" and L.ngsx_debug_get_timing(tbuf) == 0:          # mean over the timed steps (ring of 64 event sets)
         kern_ms.append(list(tbuf))
-    launches = L.ngsx_launch_count() - launches0
     L.ngsx_debug_set_timing(0)
     total_ms = t_begin.elapsed_time(t_end)
     for e in rec:                                        # per stage: from its start event to its last kernel, on its stream
@@ -368,7 +422,7 @@ def run_b200(args):
                                f"assemble-to-CSR ({n_global} HASNEG elements) + CutInfo + Integrate(IF,NEG)",
                    "ne": mesh.ne, "hasneg_elements": n_global, "nnz": nnz_global, "assembly": a.assembly, "group": args.group, "colors": plan.ncolors,
                    "setup_s_untimed": round(setup_s, 2), "stage_ms": {"classify": cl_ms, "assemble": as_ms, "integrate": in_ms},
-                   "stage_ms_one_stream": serial_break,
+                   "stage_ms_one_stream": serial_break, "launch": graph_note,
                    "streams": "1 (serial stages)" if serial else "assemble, then CutInfo.Update | Integrate(IF) | Integrate(NEG) on three streams; stage_ms = stage start to its last kernel (the three sweeps overlap)",
                    "l2": "inputs larger than L2 (CSR values + pair descriptors + mesh > 1.4 GB touched per step vs 126 MB L2); no explicit flush",
                    "partition": "owner-computes: contiguous chunks of equal cost (cut element = 3.2 uncut) of the HASNEG element list per rank, a CSR row belongs to the rank of the first listed element touching it, halo elements re-evaluated, no interface-row exchange; element blocks for Integrate, scalars all-reduced (NCCL)"},

@@ -1116,10 +1116,7 @@ int ngsx_assemble_csr_rows_h1(const ngsx_mesh *mesh, const double *lset_v, int f
   const int nd = dim == 2 ? (fe_order == 1 ? 3 : 6) : (fe_order == 1 ? 4 : 10);
   NGSX_REQUIRE(nd == plan->nd, "assemble_csr_rows_h1: the plan was built for another element type");
   cudaStream_t st = as_stream(stream);
-  if (err) {
-    int64_t init[2] = {0, INT64_MAX};
-    NGSX_CUDA(cudaMemcpyAsync(err, init, sizeof init, cudaMemcpyHostToDevice, st));
-  }
+  if (err) { if (int rc = reset_err(err, st)) return rc; }
   if (nlist == 0 || plan->nrows == 0) return NGSX_OK;
   if (int rc = rows_scratch(plan, npairtab)) return rc;
   FormDev form;

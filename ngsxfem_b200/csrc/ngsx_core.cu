@@ -176,6 +176,15 @@ __device__ __forceinline__ void load_element(const ngsx_mesh &M, const double *_
   }
 }
 
+// {count, first element} record of the degenerate-level-set check: reset by a kernel, not by a copy from the host stack, so that
+// every entry point of the step can be captured into a CUDA graph
+__global__ void k_reset_err(int64_t *err) { err[0] = 0; err[1] = INT64_MAX; }
+int reset_err(int64_t *err, cudaStream_t st) {
+  k_reset_err<<<1, 1, 0, st>>>(err);
+  NGSX_CUDA(cudaGetLastError());
+  return NGSX_OK;
+}
+
 __global__ void k_clamp(int64_t n, const double *__restrict__ in, double eps, double *__restrict__ out) {
   int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= n) return;
@@ -780,10 +789,7 @@ int ngsx_classify(const ngsx_mesh *mesh, const double *lset_v, uint32_t *cdom_wo
   const DeviceData *dd = device_data();
   if (!dd) return NGSX_ERR_CUDA;
   cudaStream_t st = as_stream(stream);
-  if (err) {
-    int64_t init[2] = {0, INT64_MAX};
-    NGSX_CUDA(cudaMemcpyAsync(err, init, sizeof init, cudaMemcpyHostToDevice, st));
-  }
+  if (err) { if (int rc = reset_err(err, st)) return rc; }
   if (mesh->ne == 0) return NGSX_OK;
   int64_t nwords = (mesh->ne + 31) / 32;
   auto *e = reinterpret_cast<unsigned long long *>(err);
@@ -843,10 +849,7 @@ int ngsx_rule_count(const ngsx_mesh *mesh, const double *lset_v, int dt, int ord
   int nv, ni;
   if (int rc = lookup_rules(dd, mesh->dim, order, &rv, &nv, &ri, &ni)) return rc;
   cudaStream_t st = as_stream(stream);
-  if (err) {
-    int64_t init[2] = {0, INT64_MAX};
-    NGSX_CUDA(cudaMemcpyAsync(err, init, sizeof init, cudaMemcpyHostToDevice, st));
-  }
+  if (err) { if (int rc = reset_err(err, st)) return rc; }
   if (mesh->ne == 0) return NGSX_OK;
   auto *e = reinterpret_cast<unsigned long long *>(err);
   if (mesh->dim == 2) k_rule_count<2><<<nblocks(mesh->ne, 256), 256, 0, st>>>(*mesh, lset_v, dd->cut_table, dt, nv, ni, npts, e);

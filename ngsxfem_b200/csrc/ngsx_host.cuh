@@ -11,6 +11,7 @@
 namespace ngsx {
 
 void set_error(const std::string &msg);
+int reset_err(int64_t *err, cudaStream_t st);      // {count, first} record of the degenerate-level-set check -> {0, INT64_MAX}
 extern std::atomic<int64_t> g_launches;
 
 #define NGSX_CUDA(call)                                                                              \
