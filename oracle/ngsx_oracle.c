@@ -531,6 +531,171 @@ int orc_elvec_h1(int dim, int fe_order, const int *vnums, const double *pmat, co
   return np;
 }
 
+/* ------------------------------------------------------------------ deformed (isoparametric) elements, SURVEY 8 f-4 */
+/* mesh.SetDeformation(gf) (NGS/comp/meshaccess.cpp ALE_ElementTransformation: point and Jacobian of the base
+ * transformation plus the deformation field and its reference gradient) == FE_ElementTransformation with the H1 element of
+ * the deformation's order and pointmat = coefficients of x(xi) in that basis (NGS/fem/elementtransformation.cpp
+ * CalcJacobian: dxdxi = pointmat * dshape; CalcPoint: pointmat * shape):
+ *   gcoef[ndg][dim]: vertex dofs = vertex coordinates + deformation, edge dofs (order 2) = deformation.
+ * out: x, J[r][k] = dx_r/dxi_k, Jinv, det */
+static void iso_eval(int dim, int dord, const double *gcoef, const double *xi, double *x, double J[3][3], double Jinv[3][3], double *det)
+{
+  double sh[ORC_MAXND], dsh[ORC_MAXND*3];
+  int ndg = orc_h1_shape(dim, dord, 0, xi, sh, dsh);
+  double pm[12];
+  affine_t A;
+  memset(J, 0, 9*sizeof(double));
+  for (int r = 0; r < 3; r++) x[r] = 0;
+  for (int i = 0; i < ndg; i++)
+    for (int r = 0; r < dim; r++) {
+      x[r] += gcoef[i*dim + r] * sh[i];
+      for (int k = 0; k < dim; k++) J[r][k] += gcoef[i*dim + r] * dsh[i*dim + k];
+    }
+  /* reuse the affine inverse (NGS/basiclinalg CalcInverse) on a simplex whose edge vectors are the columns of J */
+  for (int k = 0; k < dim; k++) for (int r = 0; r < dim; r++) pm[k*dim + r] = J[r][k];
+  for (int r = 0; r < dim; r++) pm[dim*dim + r] = 0.0;
+  affine_init(dim, pm, &A);
+  memcpy(Jinv, A.Jinv, sizeof A.Jinv);
+  *det = A.det;
+}
+
+/* cutint/straightcutrule.cpp:580-661 with a non-affine trafo: points/weights of the untransformed rule; IF weights times
+ * |F(xi_q)^-T n_ref| per point (:558-576).  Also returns per point the measure |det F| and the mapped point. */
+int orc_cut_rule_iso(int dim, int dord, const double *gcoef, const double *ls, int dt, int order,
+                     double *pts3, double *wts, double *meas, double *xphys, int cap)
+{
+  int n = orc_cut_rule_untrafo(dim, ls, dt, order, pts3, wts, cap);
+  if (n < 0) return n;
+  int iface = dt == IF && orc_check_straight_cut(dim + 1, ls) == IF;
+  double nr[3];
+  if (iface) lset_ref_normal(dim, ls, nr);
+  for (int q = 0; q < n; q++) {
+    double x[3], J[3][3], Ji[3][3], det;
+    iso_eval(dim, dord, gcoef, pts3 + 3*q, x, J, Ji, &det);
+    if (iface) {
+      double v[3] = {0, 0, 0};
+      for (int r = 0; r < dim; r++)
+        for (int k = 0; k < dim; k++) v[r] += Ji[k][r] * nr[k];
+      wts[q] *= sqrt(v[0]*v[0] + v[1]*v[1] + v[2]*v[2]);
+    }
+    if (meas) meas[q] = fabs(det);
+    if (xphys) for (int r = 0; r < 3; r++) xphys[3*q + r] = x[r];
+  }
+  return n;
+}
+
+/* xfem/symboliccutbfi.cpp:73-315 on a deformed element.  form[8] = {c_mass, c_stiff, c_nitsche, c_dndn, hpow_mass, hpow_stiff,
+ * hpow_nitsche, hpow_dndn}: c_m u v + c_s grad u.grad v + c_n ((grad u.n) v + (grad v.n) u) + c_d (grad u.n)(grad v.n),
+ * n = grad(lset)/|grad(lset)| evaluated per point on the deformed element (a GridFunction CF), h = specialcf.mesh_size =
+ * |det F|^(1/dim): flagged ElementwiseConstant, so the reference evaluates it at the FIRST point of the rule only (:205-214). */
+int orc_elmat_h1_iso(int dim, int fe_order, int dord, const double *gcoef, const double *ls, int dt, int intorder,
+                     const double *form, double *elmat)
+{
+  static _Thread_local double pts[3*ORC_MAXPTS], w[ORC_MAXPTS], meas[ORC_MAXPTS];
+  int np = orc_cut_rule_iso(dim, dord, gcoef, ls, dt, intorder, pts, w, meas, 0, ORC_MAXPTS);
+  int nd = orc_h1_ndof(dim, fe_order);
+  if (np < 0) return np;
+  for (int i = 0; i < nd*nd; i++) elmat[i] = 0;
+  double c[4] = {form[0], form[1], form[2], form[3]};
+  if (np > 0) {
+    double h = pow(meas[0], 1.0 / dim);
+    for (int t = 0; t < 4; t++) {
+      int p = (int)form[4 + t];
+      double f = 1.0, b = p < 0 ? 1.0 / h : h;
+      for (int k = 0; k < abs(p); k++) f *= b;
+      c[t] *= f;
+    }
+  }
+  double shape[ORC_MAXND], dref[ORC_MAXND*3], dphys[ORC_MAXND*3], dn[ORC_MAXND];
+  for (int q = 0; q < np; q++) {
+    double x[3], J[3][3], Ji[3][3], det, n[3] = {0, 0, 0};
+    iso_eval(dim, dord, gcoef, pts + 3*q, x, J, Ji, &det);
+    if (orc_h1_shape(dim, fe_order, 0, pts + 3*q, shape, dref) < 0) return ORC_UNSUP;
+    for (int i = 0; i < nd; i++)
+      for (int d = 0; d < dim; d++) {
+        double v = 0;
+        for (int k = 0; k < dim; k++) v += dref[i*dim + k] * Ji[k][d];
+        dphys[i*dim + d] = v;
+      }
+    double g2 = 0;
+    for (int d = 0; d < dim; d++) {
+      for (int k = 0; k < dim; k++) n[d] += (ls[k] - ls[dim]) * Ji[k][d];      /* grad of the P1 level set */
+      g2 += n[d]*n[d];
+    }
+    for (int d = 0; d < dim; d++) n[d] /= sqrt(g2);
+    for (int i = 0; i < nd; i++) {
+      dn[i] = 0;
+      for (int d = 0; d < dim; d++) dn[i] += dphys[i*dim + d] * n[d];
+    }
+    double fac = meas[q] * w[q];
+    for (int i = 0; i < nd; i++)
+      for (int j = 0; j < nd; j++) {
+        double g = 0;
+        for (int d = 0; d < dim; d++) g += dphys[i*dim + d] * dphys[j*dim + d];
+        elmat[i*nd + j] += fac * (c[1] * g + c[0] * shape[i] * shape[j] + c[2] * (dn[j]*shape[i] + dn[i]*shape[j]) + c[3] * dn[i]*dn[j]);
+      }
+  }
+  return np;
+}
+
+/* coefficients of x(xi) on element e: vertex coordinates + deformation on the vertex dofs, deformation on the others */
+static void gather_iso(int dim, const int32_t *el2v, const double *vert, const double *lset_v, int ndg, const int32_t *el2dof_def,
+                       const double *defo, int64_t e, double *gcoef, double *ls)
+{
+  int nv = dim + 1;
+  for (int i = 0; i < ndg; i++) {
+    int64_t g = el2dof_def[e*ndg + i];
+    for (int d = 0; d < dim; d++) gcoef[i*dim + d] = defo[g*dim + d];
+  }
+  for (int i = 0; i < nv; i++) {
+    int64_t v = el2v[e*nv + i];
+    ls[i] = lset_v[v];
+    for (int d = 0; d < dim; d++) gcoef[i*dim + d] += vert[v*dim + d];
+  }
+}
+
+/* IntegrateX (cutint/python_cutint.cpp:20-72) on a deformed mesh, cf = polynomial in the mapped point */
+double orc_integrate_mesh_iso(int dim, int64_t ne, const int32_t *el2v, const double *vert, const double *lset_v,
+                              int dord, const int32_t *el2dof_def, const double *defo, int dt, int order,
+                              int nmono, const double *mono, int64_t *npts_total)
+{
+  double sum = 0;
+  int64_t nptot = 0;
+  int ndg = orc_h1_ndof(dim, dord);
+#pragma omp parallel for schedule(static) reduction(+:sum,nptot)
+  for (int64_t e = 0; e < ne; e++) {
+    static _Thread_local double pts[3*ORC_MAXPTS], w[ORC_MAXPTS], meas[ORC_MAXPTS], xp[3*ORC_MAXPTS];
+    double gcoef[ORC_MAXND*3], ls[4];
+    gather_iso(dim, el2v, vert, lset_v, ndg, el2dof_def, defo, e, gcoef, ls);
+    int np = orc_cut_rule_iso(dim, dord, gcoef, ls, dt, order, pts, w, meas, xp, ORC_MAXPTS);
+    if (np < 0) continue;
+    double lsum = 0;
+    for (int q = 0; q < np; q++) lsum += meas[q] * w[q] * eval_mono(nmono, mono, xp + 3*q);
+    sum += lsum;
+    nptot += np;
+  }
+  if (npts_total) *npts_total = nptot;
+  return sum;
+}
+
+int64_t orc_elmat_mesh_iso(int dim, int64_t nel, const int64_t *els, const int32_t *el2v, const double *vert, const double *lset_v,
+                           int dord, const int32_t *el2dof_def, const double *defo, int fe_order, int dt, int intorder,
+                           const double *form, double *elmats, int32_t *npts)
+{
+  int nd = orc_h1_ndof(dim, fe_order), ndg = orc_h1_ndof(dim, dord);
+  int64_t nn = 0;
+#pragma omp parallel for schedule(dynamic,256) reduction(+:nn)
+  for (int64_t k = 0; k < nel; k++) {
+    int64_t e = els ? els[k] : k;
+    double gcoef[ORC_MAXND*3], ls[4];
+    gather_iso(dim, el2v, vert, lset_v, ndg, el2dof_def, defo, e, gcoef, ls);
+    int r = orc_elmat_h1_iso(dim, fe_order, dord, gcoef, ls, dt, intorder, form, elmats + (size_t)k*nd*nd);
+    if (npts) npts[k] = r;
+    if (r < 0) memset(elmats + (size_t)k*nd*nd, 0, sizeof(double)*nd*nd); else nn++;
+  }
+  return nn;
+}
+
 /* ------------------------------------------------------------------ mesh-level loops */
 static void gather_el(int dim, const int32_t *el2v, const double *vert, const double *lset_v, int64_t e, double *pmat, double *ls, int *vn)
 {

@@ -65,6 +65,12 @@ def load():
     L.orc_elements_with_neighbor_facets.argtypes = [c_i64, c_i64, ip, ubp, ubp]
     L.orc_dofs_of_elements.argtypes = [c_i64, c_int, c_i64, ip, ubp, ubp]
     L.orc_facetpatch_elmat_h1.argtypes = [c_int, c_int, ip, dp, ip, dp, c_double, c_int, dp]
+    L.orc_cut_rule_iso.argtypes = [c_int, c_int, dp, dp, c_int, c_int, dp, dp, dp, dp, c_int]
+    L.orc_elmat_h1_iso.argtypes = [c_int, c_int, c_int, dp, dp, c_int, c_int, dp, dp]
+    L.orc_integrate_mesh_iso.argtypes = [c_int, c_i64, ip, dp, dp, c_int, ip, dp, c_int, c_int, c_int, dp, lp]
+    L.orc_integrate_mesh_iso.restype = c_double
+    L.orc_elmat_mesh_iso.argtypes = [c_int, c_i64, lp, ip, dp, dp, c_int, ip, dp, c_int, c_int, c_int, dp, dp, ip]
+    L.orc_elmat_mesh_iso.restype = c_i64
     L.orc_set_threads.argtypes = [c_int]
     _LIB = L
     return L
@@ -304,3 +310,57 @@ def dofs_of_elements(el2dof, ndof, a):
     out = np.zeros(ndof, dtype=np.uint8)
     load().orc_dofs_of_elements(e2d.shape[0], e2d.shape[1], ndof, P(e2d, ip), P(a, ubp), P(out, ubp))
     return out.astype(bool)
+
+
+# ----------------------------------------------------------------------------- deformed (isoparametric) elements, f-4
+def form8(c_mass=0.0, c_stiff=0.0, c_nitsche=0.0, c_dndn=0.0, hpow=(0, 0, 0, 0)):
+    return _d([c_mass, c_stiff, c_nitsche, c_dndn] + [float(p) for p in hpow])
+
+
+def cut_rule_iso(dim, dord, gcoef, lset, dt, order, impl="oracle", cap=2048):
+    """points, weights (IF: times |F^-T n| per point), measure |det F| and mapped point per rule point"""
+    pts = np.zeros((cap, 3)); w = np.zeros(cap); meas = np.zeros(cap); xp = np.zeros((cap, 3))
+    gc = _d(gcoef); ls = _d(lset)
+    if impl == "oracle":
+        n = load().orc_cut_rule_iso(dim, dord, P(gc), P(ls), dt, order, P(pts), P(w), P(meas), P(xp), cap)
+    else:
+        from . import refload
+        n = refload.load().ref_cut_rule_iso(ET[dim], dord, P(gc), P(ls), dt, order, P(pts), P(w), P(meas), P(xp), cap)
+    if n < 0:
+        return n, None, None, None, None
+    return n, pts[:n], w[:n], meas[:n], xp[:n]
+
+
+def elmat_h1_iso(dim, fe_order, dord, gcoef, lset, dt, intorder, form, impl="oracle"):
+    nd = load().orc_h1_ndof(dim, fe_order)
+    em = np.zeros((nd, nd))
+    gc = _d(gcoef); ls = _d(lset); f = _d(form)
+    if impl == "oracle":
+        n = load().orc_elmat_h1_iso(dim, fe_order, dord, P(gc), P(ls), dt, intorder, P(f), P(em))
+    else:
+        from . import refload
+        assert f[2] == 0 and f[3] == 0 and not f[4:].any(), "the compiled-reference driver restates mass + stiffness only"
+        n = refload.load().ref_elmat_h1_iso(ET[dim], fe_order, dord, P(gc), P(ls), dt, intorder, f[0], f[1], P(em))
+    return n, em
+
+
+def integrate_mesh_iso(dim, el2v, vert, lset_v, dord, el2dof_def, defo, dt, order, mono=None, nthreads=0):
+    ev = _i(el2v); vt = _d(vert); ls = _d(lset_v); ed = _i(el2dof_def); df = _d(defo); mo = mono_array(mono)
+    load().orc_set_threads(nthreads)
+    npt = c_i64(0)
+    val = load().orc_integrate_mesh_iso(dim, ev.shape[0], P(ev, ip), P(vt), P(ls), dord, P(ed, ip), P(df), dt, order, len(mo), P(mo),
+                                        ctypes.byref(npt))
+    return val, npt.value
+
+
+def elmat_mesh_iso(dim, el2v, vert, lset_v, dord, el2dof_def, defo, fe_order, dt, intorder, form, els=None, nthreads=0):
+    ev = _i(el2v); vt = _d(vert); ls = _d(lset_v); ed = _i(el2dof_def); df = _d(defo); f = _d(form)
+    nd = load().orc_h1_ndof(dim, fe_order)
+    load().orc_set_threads(nthreads)
+    if els is None:
+        nel, ep = ev.shape[0], None
+    else:
+        ee = np.ascontiguousarray(els, dtype=np.int64); nel, ep = len(ee), P(ee, lp)
+    out = np.zeros((nel, nd, nd)); npts = np.zeros(nel, dtype=np.int32)
+    load().orc_elmat_mesh_iso(dim, nel, ep, P(ev, ip), P(vt), P(ls), dord, P(ed, ip), P(df), fe_order, dt, intorder, P(f), P(out), P(npts, ip))
+    return out, npts

@@ -62,6 +62,94 @@ const IntegrationRule * TrafoRule(ELEMENT_TYPE et, const double * pmat, const do
   return StraightCutIntegrationRule(lv, *trafo, DOMAIN_TYPE(dt), order, FIND_OPTIMAL, lh);
 }
 
+// isoparametric transformation: FE_ElementTransformation with the reference's H1HighOrderFE of order dord as the
+// geometry element and pointmat = gcoef^T (NGS/fem/elementtransformation.hpp:199-260: SetElement + PointMatrix; CalcJacobian
+// = pointmat * dshape).  This is what mesh.SetDeformation amounts to per element (base point + deformation field).
+template <ELEMENT_TYPE ET>
+FE_ElementTransformation<ET_trait<ET>::DIM, ET_trait<ET>::DIM> * IsoTrafo(int dord, const double * gcoef, LocalHeap & lh)
+{
+  constexpr int D = ET_trait<ET>::DIM;
+  auto gfel = new (lh) H1HighOrderFE<ET>(dord);
+  auto trafo = new (lh) FE_ElementTransformation<D,D>();
+  trafo->SetElement(gfel, 0, 0);
+  int ndg = gfel->GetNDof();
+  auto pm = trafo->PointMatrix();
+  for (int i = 0; i < ndg; i++) for (int d = 0; d < D; d++) pm(d, i) = gcoef[i*D+d];
+  return trafo;
+}
+
+template <ELEMENT_TYPE ET>
+int RuleIso(int dord, const double * gcoef, const double * lset, int dt, int order,
+            double * pts3, double * wts, double * meas, double * xphys, int cap, LocalHeap & lh)
+{
+  constexpr int D = ET_trait<ET>::DIM;
+  auto trafo = IsoTrafo<ET>(dord, gcoef, lh);
+  Vector<> lv(D+1);
+  for (int i = 0; i < D+1; i++) lv(i) = lset[i];
+  const IntegrationRule * ir = StraightCutIntegrationRule(lv, *trafo, DOMAIN_TYPE(dt), order, FIND_OPTIMAL, lh);
+  int n = CopyRule(ir, pts3, wts, cap);
+  if (n < 0) return n;
+  MappedIntegrationRule<D,D> mir(*ir, *trafo, lh);
+  for (int i = 0; i < n; i++)
+    {
+      meas[i] = mir[i].GetMeasure();
+      for (int d = 0; d < 3; d++) xphys[3*i+d] = d < D ? mir[i].GetPoint()(d) : 0.0;
+    }
+  return n;
+}
+
+// as ElmatWork::Elmat below, on the isoparametric transformation
+template <ELEMENT_TYPE ET>
+int ElmatIso(int fe_order, int dord, const double * gcoef, const double * lset, int dt, int intorder,
+             double c_mass, double c_stiff, double * elmat_out, LocalHeap & lh)
+{
+  constexpr int D = ET_trait<ET>::DIM;
+  H1HighOrderFE<ET> fel(fe_order);
+  int nd = fel.GetNDof();
+  auto trafo = IsoTrafo<ET>(dord, gcoef, lh);
+  Vector<> lv(D+1);
+  for (int i = 0; i < D+1; i++) lv(i) = lset[i];
+  const IntegrationRule * ir = StraightCutIntegrationRule(lv, *trafo, DOMAIN_TYPE(dt), intorder, FIND_OPTIMAL, lh);
+  if (!ir) return -1;
+  int np = ir->Size();
+  MappedIntegrationRule<D,D> mir(*ir, *trafo, lh);
+  FlatMatrix<> elmat(nd, nd, lh); elmat = 0.0;
+  constexpr int BS = 16;
+  for (int pass = 0; pass < 2; pass++)
+    {
+      double coef = pass == 0 ? c_stiff : c_mass;
+      if (coef == 0.0) continue;
+      int pd = pass == 0 ? D : 1;
+      for (int i0 = 0; i0 < np; i0 += BS)
+        {
+          HeapReset hr2(lh);
+          int bs = min2(BS, np - i0);
+          FlatMatrix<> bbmat(nd, bs*pd, lh), bdbmat(nd, bs*pd, lh);
+          for (int j = 0; j < bs; j++)
+            {
+              int ii = i0 + j;
+              double dval = coef * mir[ii].GetMeasure() * (*ir)[ii].Weight();
+              if (pass == 0)
+                {
+                  FlatMatrixFixWidth<D> dshape(nd, lh);
+                  fel.CalcMappedDShape(mir[ii], dshape);
+                  for (int k = 0; k < nd; k++) for (int d = 0; d < D; d++)
+                    { bbmat(k, j*D+d) = dshape(k,d); bdbmat(k, j*D+d) = dval * dshape(k,d); }
+                }
+              else
+                {
+                  FlatVector<> shape(nd, lh);
+                  fel.CalcShape((*ir)[ii], shape);
+                  for (int k = 0; k < nd; k++) { bbmat(k, j) = shape(k); bdbmat(k, j) = dval * shape(k); }
+                }
+            }
+          AddABt(bbmat, bdbmat, elmat);
+        }
+    }
+  for (int i = 0; i < nd; i++) for (int j = 0; j < nd; j++) elmat_out[i*nd+j] = elmat(i,j);
+  return np;
+}
+
 template <ELEMENT_TYPE ET>
 struct ElmatWork
 {
@@ -183,6 +271,30 @@ int ref_cut_rule(int et, const double * pmat, const double * lset, int dt, int o
     else if (et == ET_TET) { FE_ElementTransformation<3,3> * t; ir = TrafoRule<3>(ET_TET, pmat, lset, dt, order, lh, t); }
     else return -4;
     return CopyRule(ir, pts3, wts, cap);
+  } catch (...) { return -2; }
+}
+
+// deformed element: StraightCutIntegrationRule on an isoparametric trafo (IF weights: per-point |F^-T n|,
+// cutint/straightcutrule.cpp:558-576), measure and mapped point of every rule point
+int ref_cut_rule_iso(int et, int dord, const double * gcoef, const double * lset, int dt, int order,
+                     double * pts3, double * wts, double * meas, double * xphys, int cap)
+{
+  LocalHeap & lh = GetLH(); HeapReset hr(lh);
+  try {
+    if (et == ET_TRIG) return RuleIso<ET_TRIG>(dord, gcoef, lset, dt, order, pts3, wts, meas, xphys, cap, lh);
+    if (et == ET_TET) return RuleIso<ET_TET>(dord, gcoef, lset, dt, order, pts3, wts, meas, xphys, cap, lh);
+    return -4;
+  } catch (...) { return -2; }
+}
+
+int ref_elmat_h1_iso(int et, int fe_order, int dord, const double * gcoef, const double * lset, int dt, int intorder,
+                     double c_mass, double c_stiff, double * elmat)
+{
+  LocalHeap & lh = GetLH(); HeapReset hr(lh);
+  try {
+    if (et == ET_TRIG) return ElmatIso<ET_TRIG>(fe_order, dord, gcoef, lset, dt, intorder, c_mass, c_stiff, elmat, lh);
+    if (et == ET_TET) return ElmatIso<ET_TET>(fe_order, dord, gcoef, lset, dt, intorder, c_mass, c_stiff, elmat, lh);
+    return -4;
   } catch (...) { return -2; }
 }
 

@@ -49,3 +49,59 @@ def test_shapes_and_elmat_random(dim, fo):
             assert a[0] == b[0]
             if a[0] > 0:
                 assert np.abs(a[1] - b[1]).max() <= 1e-12 * np.abs(b[1]).max()
+
+
+def iso_coefs(rng, dim, dord, amp=0.08):
+    """coefficients of x(xi) in the H1 basis of order dord: a nice simplex, perturbed vertices, curved edges (order 2)"""
+    pm = nice_simplex(rng, dim)
+    h = np.abs(np.linalg.det(pm[:dim] - pm[dim])) ** (1.0 / dim)
+    nd = orc.load().orc_h1_ndof(dim, dord)
+    gc = np.zeros((nd, dim))
+    gc[:dim + 1] = pm
+    gc += amp * h * rng.uniform(-1, 1, (nd, dim)) * (4.0 if dord == 2 else 1.0) * (np.arange(nd)[:, None] > dim if dord == 2 else 1.0)
+    return gc
+
+
+@pytest.mark.parametrize("dim", [2, 3])
+@pytest.mark.parametrize("dord", [1, 2])
+def test_deformed_rule_and_elmat_random(dim, dord):
+    """the isoparametric restatement (orc_cut_rule_iso / orc_elmat_h1_iso) against the reference's own
+    StraightCutIntegrationRule + MappedIntegrationRule + H1HighOrderFE on an FE_ElementTransformation whose geometry element
+    is the order-dord H1 element (what mesh.SetDeformation amounts to on one element)."""
+    rng = np.random.default_rng(100 * dim + dord)
+    for t in range(120):
+        gc = iso_coefs(rng, dim, dord)
+        ls = rng.uniform(-1, 1, dim + 1)
+        for dt in (0, 1, 2):
+            for order in (2, 4):
+                a = orc.cut_rule_iso(dim, dord, gc, ls, dt, order)
+                b = orc.cut_rule_iso(dim, dord, gc, ls, dt, order, impl="ref")
+                assert a[0] == b[0]
+                if a[0] > 0:
+                    assert np.abs(a[1] - b[1]).max() <= 1e-14
+                    assert np.abs(a[2] - b[2]).max() <= 1e-12 * np.abs(b[2]).max()
+                    assert np.abs(a[3] - b[3]).max() <= 1e-12 * np.abs(b[3]).max()
+                    assert np.abs(a[4] - b[4]).max() <= 1e-13 * max(1.0, np.abs(b[4]).max())
+            for fo in (1, 2):
+                a = orc.elmat_h1_iso(dim, fo, dord, gc, ls, dt, 2 * fo, orc.form8(1.3, 0.7))
+                b = orc.elmat_h1_iso(dim, fo, dord, gc, ls, dt, 2 * fo, orc.form8(1.3, 0.7), impl="ref")
+                assert a[0] == b[0]
+                if a[0] > 0:
+                    assert np.abs(a[1] - b[1]).max() <= 1e-12 * np.abs(b[1]).max()
+
+
+@pytest.mark.parametrize("dim", [2, 3])
+def test_deformed_reduces_to_affine(dim):
+    """zero deformation: the isoparametric restatement equals the affine one"""
+    rng = np.random.default_rng(5 + dim)
+    for t in range(50):
+        pm = nice_simplex(rng, dim)
+        ls = rng.uniform(-1, 1, dim + 1)
+        for dord in (1, 2):
+            gc = np.zeros((orc.load().orc_h1_ndof(dim, dord), dim)); gc[:dim + 1] = pm
+            for dt in (0, 1, 2):
+                a = orc.elmat_h1_iso(dim, 2, dord, gc, ls, dt, 4, orc.form8(1.3, 0.7))
+                b = orc.elmat_h1(dim, 2, np.arange(dim + 1), pm, ls, dt, 4, 1.3, 0.7)
+                assert a[0] == b[0]
+                if a[0] > 0:
+                    assert np.abs(a[1] - b[1]).max() <= 1e-12 * np.abs(b[1]).max()
