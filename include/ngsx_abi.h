@@ -215,6 +215,29 @@ int ngsx_gather_vec(int64_t ndof, const int64_t *dofptr /*[ndof+1]*/, const int6
  * reproducible run to run).  out is a device double. */
 int ngsx_integrate(const ngsx_mesh *mesh, const double *lset_v, int dt, int order, const ngsx_poly *h_f, double *out, void *stream);
 
+/* ---- (f-4) deformed (isoparametric) elements -----------------------------------------------------------------------
+ * mesh.SetDeformation(gf) (NGS/comp/bilinearform.cpp:1235 picks the deformed ElementTransformation; lsetcurving/lsetcurv.py
+ * :108-163 produces gf): x(xi) = affine map + sum_i coef[el2dof[e][i]] phi_i(xi), phi = scalar H1 basis of `order` (1..2,
+ * vertex dofs then edge dofs, as el2dof of the H1 space), coef interleaved [ndof][dim] (H1(mesh, order, dim=mesh.dim)).
+ * The cut rule stays on the reference element (cutint/straightcutrule.cpp:580-661); measure, mapped gradients, interface
+ * weight factor |F^-T n_ref| (:558-576) and the level-set normal are evaluated per rule point; h = |det F|^(1/dim) at the
+ * first rule point of the element (specialcf.mesh_size is elementwise constant, xfem/symboliccutbfi.cpp:205-214). */
+typedef struct ngsx_deformation {
+  int32_t order;            /* 1 or 2 */
+  int32_t nd;               /* dofs per element and component: dim+1 (order 1), 6 / 10 (order 2) */
+  int64_t ndof;
+  const int32_t *el2dof;    /* [ne][nd] */
+  const double  *coef;      /* [ndof][dim] */
+} ngsx_deformation;
+/* batched CalcElementMatrixAdd (xfem/symboliccutbfi.cpp:73-315) on the deformed mesh; arguments as ngsx_elmat_h1, err as in
+ * ngsx_classify (may be NULL).  The dense blocks reach the CSR values through ngsx_assemble_csr_rows_mats. */
+int ngsx_elmat_h1_deformed(const ngsx_mesh *mesh, const ngsx_deformation *defo, const double *lset_v, int fe_order, int dt, int intorder,
+                           const ngsx_form_h1 *h_form, int64_t nlist, const int32_t *els, double *elmats, int32_t *npts,
+                           int64_t *err, void *stream);
+/* IntegrateX (cutint/python_cutint.cpp:20-72) on the deformed mesh: f is evaluated at the mapped points */
+int ngsx_integrate_deformed(const ngsx_mesh *mesh, const ngsx_deformation *defo, const double *lset_v, int dt, int order,
+                            const ngsx_poly *h_f, double *out, void *stream);
+
 /* ---- (f-3) space-time cut quadrature -----------------------------------------------------------------------------
  * SpaceTimeCutIntegrationRule (cutint/spacetimecutrule.cpp:98-196) for a level set that is P1 in space and nodal of order
  * ntime_dofs - 1 (0..2) in the reference time: lset_st [ntime_dofs][nv], time-major like SpaceTimeFESpace::GetDofNrs

@@ -39,6 +39,10 @@ class XTerm(ctypes.Structure):
     _fields_ = [("coef", c_double), ("hpow", c_i32), ("kappa", c_i32), ("pair", c_i32), ("blk_u", c_i32), ("blk_v", c_i32), ("_pad", c_i32)]
 
 
+class Deformation(ctypes.Structure):
+    _fields_ = [("order", c_i32), ("nd", c_i32), ("ndof", c_i64), ("el2dof", c_void_p), ("coef", c_void_p)]
+
+
 class Poly(ctypes.Structure):
     _fields_ = [("nterms", c_i32), ("_pad", c_i32), ("coef", c_double * POLY_MAXTERMS), ("ex", (c_i32 * 3) * POLY_MAXTERMS)]
 
@@ -78,6 +82,10 @@ SIGNATURES = {
     "ngsx_assemble_csr_rows_h1": (c_int, [ctypes.POINTER(Mesh), c_void_p, c_int, c_int, c_int, ctypes.POINTER(FormH1), c_i64, c_void_p,
                                           c_void_p, c_int, c_void_p, c_void_p, c_void_p]),
     "ngsx_integrate": (c_int, [ctypes.POINTER(Mesh), c_void_p, c_int, c_int, ctypes.POINTER(Poly), c_void_p, c_void_p]),
+    "ngsx_elmat_h1_deformed": (c_int, [ctypes.POINTER(Mesh), ctypes.POINTER(Deformation), c_void_p, c_int, c_int, c_int, ctypes.POINTER(FormH1),
+                                       c_i64, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p]),
+    "ngsx_integrate_deformed": (c_int, [ctypes.POINTER(Mesh), ctypes.POINTER(Deformation), c_void_p, c_int, c_int, ctypes.POINTER(Poly),
+                                        c_void_p, c_void_p]),
     "ngsx_facets_neighbor_types": (c_int, [c_i64, c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_void_p, c_void_p]),
     "ngsx_elements_with_neighbor_facets": (c_int, [c_i64, c_void_p, c_void_p, c_i64, c_void_p, c_void_p]),
     "ngsx_dofs_of_elements": (c_int, [c_i64, c_i32, c_void_p, c_void_p, c_i64, c_void_p, c_void_p]),

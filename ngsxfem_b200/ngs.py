@@ -102,6 +102,8 @@ class Mesh(SimplexMesh):
     def __init__(self, m: SimplexMesh, device="cuda"):
         super().__init__(m.dim, m.vert.to(device).contiguous(), m.el2v.to(device).contiguous())
         self._c = None
+        self.deformation = None
+        self._block = None
 
     def c_struct(self) -> _lib.Mesh:
         if self._c is None:
@@ -117,7 +119,33 @@ class Mesh(SimplexMesh):
         m = Mesh.__new__(Mesh)
         SimplexMesh.__init__(m, self.dim, self.vert, self.el2v[lo:hi])
         m._c = None
+        m.deformation, m._block = self.deformation, (lo, hi)
         return m
+
+    def SetDeformation(self, gf: "GridFunction"):
+        """MeshAccess::SetDeformation (NGS/comp/meshaccess.hpp): every ElementTransformation becomes the affine map plus the
+        vector H1 field gf (H1(mesh, order = 1..2, dim = mesh.dim)); SURVEY section 8 row f-4"""
+        if gf is not None:
+            fes = gf.space
+            if not isinstance(fes, H1) or fes.dim != self.dim or fes.order not in (1, 2):
+                raise _lib.NgsxError(-2, "deformation must be a GridFunction on H1(mesh, order = 1 or 2, dim = mesh.dim); no CPU fallback")
+        self.deformation = gf
+
+    def UnsetDeformation(self):
+        self.deformation = None
+
+    def c_deformation(self, gf: "GridFunction" = None):
+        """ngsx_deformation of gf (default: the mesh deformation), restricted to this element block; None if undeformed"""
+        gf = gf if gf is not None else self.deformation
+        if gf is None:
+            return None
+        fes = gf.space
+        el2dof = fes.el2dof if self._block is None else fes.el2dof[self._block[0]:self._block[1]]
+        coef = gf.vec.reshape(fes.ndof, self.dim)
+        require_cuda(coef, "deformation")
+        d = _lib.Deformation(fes.order, fes.nd, fes.ndof, el2dof.data_ptr(), coef.data_ptr())
+        d._keep = (el2dof, coef)
+        return d
 
     @property
     def nfacet(self):
@@ -131,8 +159,8 @@ class FESpace:
 class H1(FESpace):
     """H1HighOrderFESpace stand-in (orders 1..2 on the CUDA path)."""
 
-    def __init__(self, mesh: Mesh, order: int = 1, dgjumps: bool = False, **_):
-        self.mesh, self.order, self.dgjumps = mesh, order, dgjumps
+    def __init__(self, mesh: Mesh, order: int = 1, dgjumps: bool = False, dim: int = 1, **_):
+        self.mesh, self.order, self.dgjumps, self.dim = mesh, order, dgjumps, dim          # dim > 1: interleaved vector field
         self.el2dof, self.ndof = mesh.h1_dofs(order)
         self.nd = self.el2dof.shape[1]
 
@@ -149,7 +177,8 @@ class H1(FESpace):
 class GridFunction:
     def __init__(self, fes: H1):
         self.space = fes
-        self.vec = torch.zeros(fes.ndof, dtype=torch.float64, device=fes.mesh.device)
+        shape = fes.ndof if getattr(fes, "dim", 1) == 1 else (fes.ndof, fes.dim)
+        self.vec = torch.zeros(shape, dtype=torch.float64, device=fes.mesh.device)
 
 
 # ------------------------------------------------------------------------------------------------------------------

@@ -192,7 +192,12 @@ def IntegrateX(lset, mesh: Mesh, cf=None, order: int = 5, domain_type=IF, subdiv
     lv = _lset_vec(lset)
     out = torch.zeros(1, dtype=torch.float64, device=mesh.device)
     poly = _poly_of(cf)
-    check(_lib_().ngsx_integrate(ctypes.byref(mesh.c_struct()), _ptr(lv), int(domain_type), order, ctypes.byref(poly), _ptr(out), _stream()))
+    defo = mesh.c_deformation()
+    if defo is not None:                                             # mesh.SetDeformation(...): per-point geometry (row f-4)
+        check(_lib_().ngsx_integrate_deformed(ctypes.byref(mesh.c_struct()), ctypes.byref(defo), _ptr(lv), int(domain_type), order,
+                                              ctypes.byref(poly), _ptr(out), _stream()))
+    else:
+        check(_lib_().ngsx_integrate(ctypes.byref(mesh.c_struct()), _ptr(lv), int(domain_type), order, ctypes.byref(poly), _ptr(out), _stream()))
     return float(out.item()) if sync else out
 
 
@@ -286,12 +291,15 @@ class SymbolicCutBFI:
             raise NgsxError(-1, "form is required")
         if VOL_or_BND != VOL or element_boundary or skeleton:
             raise NgsxError(-2, "element_boundary / skeleton / BND cut integrators are outside the CUDA path")
-        if time_order >= 0 or subdivlvl != 0 or deformation is not None or definedon is not None:
-            raise NgsxError(-2, "time_order / subdivlvl / deformation / definedon are outside the CUDA path")
+        if time_order >= 0 or subdivlvl != 0 or definedon is not None:
+            raise NgsxError(-2, "time_order / subdivlvl / definedon are outside the CUDA path")
         self.lset, self.dt, self.force_intorder, self.definedonelements = lset, int(domain_type), force_intorder, definedonelements
+        self.deformation = deformation                     # bfi->SetDeformation (xfem/python_xfem.cpp:512-513); None: the mesh's
         self.xterms = None
         from . import xfes
         if xfes.has_x_atoms(form):
+            if deformation is not None:
+                raise NgsxError(-2, "a deformation on a compound [Vh, XFESpace] integrator is outside the CUDA path")
             self._init_x(form, xfes)
             return
         terms = form.collect()
@@ -673,6 +681,11 @@ class BilinearForm:
             self._build_graph()
             self._plans.clear()
             self._xshared = None
+        if fes.mesh.deformation is not None or any(getattr(i, "deformation", None) is not None for i in self.integrators):
+            for integ in self.integrators:                         # what the deformed path covers
+                if not isinstance(integ, SymbolicCutBFI) or integ.xterms is not None or self.assembly != "rows":
+                    raise NgsxError(-2, "on a deformed mesh only SymbolicCutBFI integrators on H1 through the row gather are on the "
+                                        "CUDA path (facet patches, XFESpace and the coloured scatter: undeformed only); no CPU fallback")
         plans = [self._plan_for(k, integ) for k, integ in enumerate(self.integrators)]
         # a single row plan that covers every stored entry overwrites its rows: no SetZero pass, each value written once
         # (with a row range: the rank's rows are one contiguous CSR span, the other rows belong to other ranks and stay untouched)
@@ -692,6 +705,18 @@ class BilinearForm:
                 self._assemble_facetpatch(integ, plan)
             elif integ.xterms is not None:
                 x_blocks += self._assemble_x(integ, plan, k, x_blocks)
+            elif isinstance(plan, _RowPlan) and self._deformation_of(integ) is not None:
+                # deformed elements (row f-4): per-point geometry -> dense blocks of the listed elements, then the
+                # owner-computes gather (each CSR value written once, plan order, no atomics)
+                lv = _lset_vec(integ.lset)
+                defo = fes.mesh.c_deformation(self._deformation_of(integ))
+                n = plan.els.numel()
+                if getattr(plan, "mats", None) is None:
+                    plan.mats = torch.empty((n, fes.nd * fes.nd), dtype=torch.float64, device=fes.mesh.device)
+                check(L.ngsx_elmat_h1_deformed(mesh_c, ctypes.byref(defo), _ptr(lv), fes.order, integ.dt, integ.intorder(fes.order),
+                                               ctypes.byref(integ.form), n, _ptr(plan.els), _ptr(plan.mats), None, _ptr(self._err[k]), _stream()))
+                self._err_armed = True
+                check(L.ngsx_assemble_csr_rows_mats(plan.handle, _ptr(plan.mats), 0 if overwrite else 1, _ptr(self.mat.vals), _stream()))
             elif isinstance(plan, _RowPlan):
                 lv = _lset_vec(integ.lset)
                 check(L.ngsx_assemble_csr_rows_h1(mesh_c, _ptr(lv), fes.order, integ.dt, integ.intorder(fes.order), ctypes.byref(integ.form),
@@ -706,6 +731,11 @@ class BilinearForm:
         if x_blocks:                                               # one gather for the summed blocks of all compound integrators
             check(L.ngsx_assemble_csr_rows_mats(self._xshared.handle, _ptr(self._xshared.mats), 1, _ptr(self.mat.vals), _stream()))
         return self
+
+    def _deformation_of(self, integ):
+        """the integrator's own deformation, else the mesh's (NGS/comp/bilinearform.cpp:1235)"""
+        d = getattr(integ, "deformation", None)
+        return d if d is not None else self.space.mesh.deformation
 
     def check_degenerate(self, err=None):
         """raise if the last Assemble met a level set the reference throws on; synchronises.
@@ -766,6 +796,12 @@ class BilinearForm:
         els = self._active_elements(integ).to(torch.int32).contiguous()
         out = torch.empty((els.numel(), fes.nd, fes.nd), dtype=torch.float64, device=fes.mesh.device)
         npts = torch.empty(els.numel(), dtype=torch.int32, device=fes.mesh.device)
+        if self._deformation_of(integ) is not None:
+            defo = fes.mesh.c_deformation(self._deformation_of(integ))
+            check(L.ngsx_elmat_h1_deformed(ctypes.byref(fes.mesh.c_struct()), ctypes.byref(defo), _ptr(_lset_vec(integ.lset)), fes.order, integ.dt,
+                                           integ.intorder(fes.order), ctypes.byref(integ.form), els.numel(), _ptr(els), _ptr(out), _ptr(npts),
+                                           None, _stream()))
+            return els, out, npts
         check(L.ngsx_elmat_h1(ctypes.byref(fes.mesh.c_struct()), _ptr(_lset_vec(integ.lset)), fes.order, integ.dt, integ.intorder(fes.order),
                               ctypes.byref(integ.form), els.numel(), _ptr(els), _ptr(out), _ptr(npts), _stream()))
         return els, out, npts
@@ -816,6 +852,8 @@ class LinearForm:
 
     def Assemble(self):
         """NGS/comp/linearform.cpp:209-243"""
+        if self.space.mesh.deformation is not None:
+            raise NgsxError(-2, "linear forms on a deformed mesh are outside the CUDA path (row f-4 covers BilinearForm + Integrate); no CPU fallback")
         L = _lib_()
         fes = self._h1
         if self.vec.numel() != self.space.ndof:                            # XFESpace.Update changed the number of x-dofs

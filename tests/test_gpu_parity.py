@@ -868,3 +868,168 @@ def test_full_size_properties(X):
     c.Assemble()
     assert torch.equal(b.mat.colidx, c.mat.colidx)
     assert (b.mat.vals - c.mat.vals).abs().max().item() <= RTOL * c.mat.vals.abs().max().item()
+
+
+# ------------------------------------------------------------------------------------------------------------------
+# deformed (isoparametric) elements -- mesh.SetDeformation / deformation = gf
+# ------------------------------------------------------------------------------------------------------------------
+def _deformed_setup(X, dim, dord, seed=3, amp=0.12):
+    nx = 12 if dim == 2 else 5
+    m = X.meshes.MakeStructured2DMesh(nx) if dim == 2 else X.meshes.MakeStructured3DMesh(nx)
+    mesh = X.ngs.Mesh(m)
+    gf = X.ngs.GridFunction(X.ngs.H1(mesh, order=1))
+    X.xfem.InterpolateToP1(X.ngs.SphereLevelset((0.5,) * dim, 0.33), gf)
+    rng = np.random.default_rng(seed)
+    gf.vec += dev(1e-3 * rng.uniform(-1, 1, mesh.nv))
+    Vd = X.ngs.H1(mesh, order=dord, dim=dim)
+    defo = X.ngs.GridFunction(Vd)
+    h = 1.0 / nx
+    d = amp * h * rng.uniform(-1, 1, (Vd.ndof, dim))
+    d[mesh.nv:] *= 4.0                                   # edge coefficients of the hierarchical basis (shape peaks at 1/8)
+    defo.vec.copy_(dev(d))
+    return mesh, gf, defo, Vd
+
+
+@pytest.mark.parametrize("dim", [2, 3])
+@pytest.mark.parametrize("fo", [1, 2])
+@pytest.mark.parametrize("dord", [1, 2])
+def test_deformed_elmats_against_oracle(X, dim, fo, dord):
+    from oracle import orc
+    mesh, gf, defo, Vd = _deformed_setup(X, dim, dord)
+    mesh.SetDeformation(defo)
+    Vh = X.ngs.H1(mesh, order=fo)
+    u, v = Vh.TnT()
+    n, hh, grad = X.ngs.LevelsetNormal(), X.ngs.specialcf.mesh_size, X.ngs.grad
+    el2v, vert, ls = mesh.el2v.cpu().numpy(), mesh.vert.cpu().numpy(), gf.vec.cpu().numpy()
+    forms = {NEG: (0.7 * grad(u) * grad(v) + 1.3 * u * v, orc.form8(1.3, 0.7)),
+             POS: (2.0 * grad(u) * grad(v), orc.form8(0.0, 2.0)),
+             IF: (-1.0 * (grad(u) * n) * v - 1.0 * (grad(v) * n) * u + 10.0 / hh * u * v + 0.5 * (grad(u) * n) * (grad(v) * n),
+                  orc.form8(10.0, 0.0, -1.0, 0.5, hpow=(-1, 0, 0, 0)))}
+    for dt, (form, f8) in forms.items():
+        a = X.xfem.BilinearForm(Vh)
+        a += X.xfem.SymbolicBFI(levelset_domain={"levelset": gf, "domain_type": dt}, form=form)
+        els, em, npts = a.elmats()
+        io = a.integrators[0].intorder(fo)
+        ref, rnp = orc.elmat_mesh_iso(dim, el2v, vert, ls, dord, Vd.el2dof.cpu().numpy(), defo.vec.cpu().numpy(), fo, dt, io, f8,
+                                      els=els.cpu().numpy())
+        assert len(els) > 0 and np.array_equal(npts.cpu().numpy(), np.maximum(rnp, 0))
+        assert relerr_rows(em.cpu().numpy(), ref) <= RTOL
+    # the deformation really matters on this input (guards against a kernel that ignores it)
+    mesh.UnsetDeformation()
+    a = X.xfem.BilinearForm(Vh)
+    a += X.xfem.SymbolicBFI(levelset_domain={"levelset": gf, "domain_type": NEG}, form=forms[NEG][0])
+    _, em0, _ = a.elmats()
+    ref, _ = orc.elmat_mesh_iso(dim, el2v, vert, ls, dord, Vd.el2dof.cpu().numpy(), defo.vec.cpu().numpy(), fo, NEG, 2 * fo, forms[NEG][1],
+                                els=a._active_elements(a.integrators[0]).cpu().numpy())
+    assert relerr_rows(em0.cpu().numpy(), ref) > 1e-3
+
+
+@pytest.mark.parametrize("dim", [2, 3])
+@pytest.mark.parametrize("dord", [1, 2])
+def test_deformed_assemble_and_integrate(X, dim, dord):
+    import scipy.sparse as sp
+    from oracle import orc
+    fo = 2
+    mesh, gf, defo, Vd = _deformed_setup(X, dim, dord, seed=11)
+    Vh = X.ngs.H1(mesh, order=fo)
+    u, v = Vh.TnT()
+    grad = X.ngs.grad
+    el2v, vert, ls = mesh.el2v.cpu().numpy(), mesh.vert.cpu().numpy(), gf.vec.cpu().numpy()
+    e2dd, dv = Vd.el2dof.cpu().numpy(), defo.vec.cpu().numpy()
+    form = 0.7 * grad(u) * grad(v) + 1.3 * u * v
+    ci = X.xfem.CutInfo(mesh, gf)
+    for dt in (NEG, IF):
+        # (1) the mesh deformation, restricted operator (the bench's shape of problem)
+        mesh.SetDeformation(defo)
+        a = X.xfem.RestrictedBilinearForm(Vh, element_restriction=ci.GetElementsOfType(X.xfem.HASNEG))
+        a += X.xfem.SymbolicBFI(levelset_domain={"levelset": gf, "domain_type": dt}, form=form)
+        a.Assemble()
+        a.check_degenerate()
+        first = a.mat.vals.clone()
+        a.mat.vals.fill_(float("nan"))
+        a.Assemble()
+        assert torch.equal(first, a.mat.vals)                                   # bitwise reproducible
+        els = a._plans[0].els.cpu().numpy()
+        ref, _ = orc.elmat_mesh_iso(dim, el2v, vert, ls, dord, e2dd, dv, fo, dt, 2 * fo, orc.form8(1.3, 0.7), els=els)
+        e2d = Vh.el2dof.cpu().numpy()[els]
+        nd = e2d.shape[1]
+        rows = np.repeat(e2d, nd, axis=1).reshape(-1); cols = np.tile(e2d, (1, nd)).reshape(-1)
+        want = sp.csr_matrix((ref.reshape(-1), (rows, cols)), shape=(Vh.ndof, Vh.ndof))
+        diff = abs(a.mat.to_scipy() - want)
+        assert diff.max() <= RTOL * abs(want).max()
+        # (2) the same through the integrator's own deformation on the undeformed mesh
+        mesh.UnsetDeformation()
+        b = X.xfem.RestrictedBilinearForm(Vh, element_restriction=ci.GetElementsOfType(X.xfem.HASNEG))
+        b += X.xfem.SymbolicBFI(levelset_domain={"levelset": gf, "domain_type": dt}, form=form, deformation=defo)
+        b.Assemble()
+        assert torch.equal(b.mat.vals, first)
+        # (3) a zero deformation reproduces the affine path
+        zero = X.ngs.GridFunction(Vd)
+        c = X.xfem.RestrictedBilinearForm(Vh, element_restriction=ci.GetElementsOfType(X.xfem.HASNEG))
+        c += X.xfem.SymbolicBFI(levelset_domain={"levelset": gf, "domain_type": dt}, form=form, deformation=zero)
+        c.Assemble()
+        d = X.xfem.RestrictedBilinearForm(Vh, element_restriction=ci.GetElementsOfType(X.xfem.HASNEG))
+        d += X.xfem.SymbolicBFI(levelset_domain={"levelset": gf, "domain_type": dt}, form=form)
+        d.Assemble()
+        assert (c.mat.vals - d.mat.vals).abs().max().item() <= RTOL * d.mat.vals.abs().max().item()
+    # Integrate on the deformed mesh vs the oracle, polynomial integrand evaluated at the mapped points
+    mesh.SetDeformation(defo)
+    x, y = X.ngs.x, X.ngs.y
+    cf, mono = 1.0 + 2.0 * x * y + y * y, [(1.0, 0, 0, 0), (2.0, 1, 1, 0), (1.0, 0, 2, 0)]
+    for dt in (NEG, POS, IF):
+        got = X.xfem.Integrate(levelset_domain={"levelset": gf, "domain_type": dt}, cf=cf, mesh=mesh, order=4)
+        again = X.xfem.Integrate(levelset_domain={"levelset": gf, "domain_type": dt}, cf=cf, mesh=mesh, order=4)
+        want, _ = orc.integrate_mesh_iso(dim, el2v, vert, ls, dord, e2dd, dv, dt, 4, mono)
+        assert got == again and abs(got - want) <= 1e-12 * abs(want)
+    # element blocks (the per-rank view of Integrate) carry the deformation
+    half = mesh.ne // 2
+    parts = [X.xfem.Integrate(levelset_domain={"levelset": gf, "domain_type": IF}, cf=cf, mesh=mesh.element_block(lo, hi), order=4)
+             for lo, hi in ((0, half), (half, mesh.ne))]
+    want, _ = orc.integrate_mesh_iso(dim, el2v, vert, ls, dord, e2dd, dv, IF, 4, mono)
+    assert abs(sum(parts) - want) <= 1e-12 * abs(want)
+    mesh.UnsetDeformation()
+
+
+@pytest.mark.parametrize("dim", [2, 3])
+def test_deformed_similarity_map_scales_integrals(X, dim):
+    """closed form: the deformation d(x) = (s R - I) x (a similarity, exactly representable in P1) scales volumes by s^dim and the
+    interface measure by s^(dim-1) -- pins the per-point |F^-T n| factor of cutint/straightcutrule.cpp:558-576 without any oracle"""
+    nx = 10 if dim == 2 else 4
+    m = X.meshes.MakeStructured2DMesh(nx) if dim == 2 else X.meshes.MakeStructured3DMesh(nx)
+    mesh = X.ngs.Mesh(m)
+    gf = X.ngs.GridFunction(X.ngs.H1(mesh, order=1))
+    X.xfem.InterpolateToP1(X.ngs.SphereLevelset((0.5,) * dim, 0.33), gf)
+    s, th = 1.7, 0.4
+    R = np.eye(dim)
+    R[0, 0], R[0, 1], R[1, 0], R[1, 1] = np.cos(th), -np.sin(th), np.sin(th), np.cos(th)
+    vert = mesh.vert.cpu().numpy()
+    base = {dt: X.xfem.Integrate(levelset_domain={"levelset": gf, "domain_type": dt}, cf=1.0, mesh=mesh, order=2) for dt in (NEG, POS, IF)}
+    for dord in (1, 2):
+        Vd = X.ngs.H1(mesh, order=dord, dim=dim)
+        defo = X.ngs.GridFunction(Vd)
+        defo.vec[:mesh.nv] = dev(vert @ (s * R - np.eye(dim)).T)
+        mesh.SetDeformation(defo)
+        for dt in (NEG, POS, IF):
+            got = X.xfem.Integrate(levelset_domain={"levelset": gf, "domain_type": dt}, cf=1.0, mesh=mesh, order=2)
+            want = base[dt] * (s ** dim if dt != IF else s ** (dim - 1))
+            assert abs(got - want) <= 1e-12 * want
+        mesh.UnsetDeformation()
+
+
+def test_deformed_unsupported_paths_raise(X):
+    mesh, gf, defo, Vd = _deformed_setup(X, 2, 1)
+    Vh = X.ngs.H1(mesh, order=1)
+    u, v = Vh.TnT()
+    with pytest.raises(X.lib.NgsxError):                                          # scalar field as a deformation
+        mesh.SetDeformation(gf)
+    mesh.SetDeformation(defo)
+    a = X.xfem.BilinearForm(Vh)
+    a.assembly = "colored"
+    a += X.xfem.SymbolicBFI(levelset_domain={"levelset": gf, "domain_type": NEG}, form=u * v)
+    with pytest.raises(X.lib.NgsxError):                                          # the coloured scatter is undeformed only
+        a.Assemble()
+    f = X.xfem.LinearForm(Vh)
+    f += X.xfem.SymbolicLFI(levelset_domain={"levelset": gf, "domain_type": NEG}, form=1.0 * v)
+    with pytest.raises(X.lib.NgsxError):
+        f.Assemble()
+    mesh.UnsetDeformation()
