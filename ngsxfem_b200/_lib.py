@@ -119,6 +119,8 @@ def load():
         fn.argtypes = args
     lib.ngsx_debug_set_fast_path.argtypes = [c_int]
     lib.ngsx_debug_set_fast_path.restype = None
+    lib.ngsx_debug_set_deformed_warp.argtypes = [c_int]
+    lib.ngsx_debug_set_deformed_warp.restype = None
     lib.ngsx_debug_set_timing.argtypes = [c_int]
     lib.ngsx_debug_set_timing.restype = None
     lib.ngsx_debug_get_timing.argtypes = [ctypes.POINTER(c_double)]

@@ -42,8 +42,9 @@ struct DefArgs {
   PolyDevD f;
   const int32_t *els;
   double *elmats; int32_t *npts;       // element matrices
-  double *partial;                     // Integrate: one partial per element
+  double *partial;                     // Integrate: one partial per element (warp kernel) / per warp (thread kernel)
   unsigned long long *err;
+  int32_t *worklist; int32_t *wcount;  // thread-per-element passes: list positions of the cut elements, their number
 };
 
 template <int DIM>
@@ -70,8 +71,17 @@ __device__ __forceinline__ void invert(const double (*J)[DIM], double (*I)[DIM],
 }
 
 // geometry at a reference point: x, gl[k][:] = grad_x lam_k (rows of F^-1, last = minus their sum), det F
-template <int DIM, int DORD>
-__device__ __forceinline__ void iso_point(const double *__restrict__ gc, const double *lam, double *x, double (*gl)[DIM], double &det) {
+struct GcWarp {                       // coefficients of the warp's element, contiguous
+  const double *p;
+  __device__ __forceinline__ double operator()(int t) const { return p[t]; }
+};
+template <int STRIDE> struct GcThread {   // coefficients of the thread's element, thread-strided (conflict free)
+  const double *p;
+  __device__ __forceinline__ double operator()(int t) const { return p[t * STRIDE]; }
+};
+
+template <int DIM, int DORD, typename GC>
+__device__ __forceinline__ void iso_point(const GC gc, const double *lam, double *x, double (*gl)[DIM], double &det) {
   constexpr int NDG = H1<DIM, DORD>::ND;
   double glr[DIM + 1][DIM];
 #pragma unroll
@@ -91,7 +101,7 @@ __device__ __forceinline__ void iso_point(const double *__restrict__ gc, const d
     h1_shape_grad<DIM, DORD>(i, lam, glr, s, g);
 #pragma unroll
     for (int r = 0; r < DIM; r++) {
-      const double c = gc[i * DIM + r];
+      const double c = gc(i * DIM + r);
       x[r] += c * s;
 #pragma unroll
       for (int k = 0; k < DIM; k++) J[r][k] += c * g[k];
@@ -195,7 +205,7 @@ __global__ void __launch_bounds__(DW * 32) k_elmat_def(DefArgs A, int64_t count)
             for (int kk = 0; kk < DIM; kk++) last -= lam[kk];
             lam[DIM] = last;
             double x[DIM], gl[DIM + 1][DIM], det;
-            iso_point<DIM, DORD>(gc, lam, x, gl, det);
+            iso_point<DIM, DORD>(GcWarp{gc}, lam, x, gl, det);
             adet = fabs(det);
             double nrm[DIM], g2 = 0.0;
 #pragma unroll
@@ -301,7 +311,7 @@ __global__ void __launch_bounds__(DW * 32) k_int_def(DefArgs A, int64_t ne) {
           for (int kk = 0; kk < DIM; kk++) last -= lam[kk];
           lam[DIM] = last;
           double x[3] = {0.0, 0.0, 0.0}, gl[DIM + 1][DIM], det;
-          iso_point<DIM, DORD>(gc, lam, x, gl, det);
+          iso_point<DIM, DORD>(GcWarp{gc}, lam, x, gl, det);
           double scale = 1.0;
           if (iface) {
             double g2 = 0.0;
@@ -324,6 +334,277 @@ __global__ void __launch_bounds__(DW * 32) k_int_def(DefArgs A, int64_t ne) {
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) sum += __shfl_xor_sync(0xffffffffu, sum, o);
     if (lane == 0) A.partial[e] = sum;
+  }
+}
+
+// ---------------------------------------------------------------------------------------------------------------
+// THREAD PER ELEMENT (the production path).  The warp-per-element kernels above spend a warp instruction per rule point
+// with 14 of 32 lanes busy and then 100 entries x 14 points on all lanes: ~1300 FP64 warp instructions per element.  One
+// thread per element keeps the upper triangle (ND (ND+1)/2 accumulators) in registers and the geometry coefficients in
+// its shared-memory column: ~7 K thread instructions = ~220 warp instructions per element.  Cut elements (14..42 points
+// instead of 14) would stall nearly every warp (8 % of the list, 93 % of the warps), so the first pass only records them
+// in a work list (integer atomics: the order never reaches a value) and a second pass of the same code walks that list.
+// ---------------------------------------------------------------------------------------------------------------
+constexpr int TT = 128;           // threads per CTA of the thread-per-element kernels
+
+template <int DIM>
+__device__ __forceinline__ void load_vertices(const ngsx_mesh &M, int64_t e, int *v) {
+  if constexpr (DIM == 3) {
+    int4 q = __ldg(reinterpret_cast<const int4 *>(M.el2v) + e);
+    v[0] = q.x; v[1] = q.y; v[2] = q.z; v[3] = q.w;
+  } else {
+    const int32_t *q = M.el2v + 3 * e;
+    v[0] = __ldg(q); v[1] = __ldg(q + 1); v[2] = __ldg(q + 2);
+  }
+}
+
+template <int DIM, int DORD>
+__device__ __forceinline__ void load_gc_thread(const DefArgs &A, int64_t e, const int *v, double *gcs) {
+  constexpr int NDG = H1<DIM, DORD>::ND;
+#pragma unroll
+  for (int i = 0; i < NDG; i++) {
+    const int64_t g = __ldg(A.D.el2dof + e * NDG + i);
+#pragma unroll
+    for (int d = 0; d < DIM; d++) {
+      double c = __ldg(A.D.coef + g * DIM + d);
+      if (i <= DIM) c += __ldg(A.M.vert + (int64_t)v[i <= DIM ? i : 0] * DIM + d);
+      gcs[(i * DIM + d) * TT] = c;
+    }
+  }
+}
+
+template <int DIM, int ORDER, int DORD, bool CUTPASS>
+__global__ void __launch_bounds__(TT) k_elmat_def_t(DefArgs A, int64_t count) {
+  constexpr int ND = H1<DIM, ORDER>::ND, NE = ND * ND, NDG = H1<DIM, DORD>::ND, NT = ND * (ND + 1) / 2;
+  extern __shared__ __align__(16) unsigned char smem_raw[];
+  double *gcs = reinterpret_cast<double *>(smem_raw) + threadIdx.x;
+  double4 *srule_vol = reinterpret_cast<double4 *>(smem_raw + (size_t)NDG * DIM * TT * 8);
+  double4 *srule_if = srule_vol + A.nr_vol;
+  for (int i = threadIdx.x; i < A.nr_vol; i += TT) srule_vol[i] = A.rule_vol[i];
+  for (int i = threadIdx.x; i < A.nr_if; i += TT) srule_if[i] = A.rule_if[i];
+  __syncthreads();
+  const bool hp = (A.form.p[0] | A.form.p[1] | A.form.p[2] | A.form.p[3]) != 0;
+  const bool nterm = A.form.c[2] != 0.0 || A.form.c[3] != 0.0;
+  const int64_t n = CUTPASS ? (int64_t)*A.wcount : count;
+  for (int64_t w = (int64_t)blockIdx.x * TT + threadIdx.x; w < n; w += (int64_t)gridDim.x * TT) {
+    const int64_t k = CUTPASS ? (int64_t)A.worklist[w] : w;
+    const int64_t e = A.els ? A.els[k] : k;
+    int v[4];
+    load_vertices<DIM>(A.M, e, v);
+    double ls[4];
+#pragma unroll
+    for (int a = 0; a <= DIM; a++) ls[a] = __ldg(A.lset + v[a]);
+    int mask;
+    const int dom = sign_test<DIM>(ls, mask);
+    const bool cut = dom == IF;
+    double *out = A.elmats + k * NE;
+    if constexpr (!CUTPASS) {
+      if (dom < 0 && A.err) {
+        atomicAdd(&A.err[0], 1ULL);
+        atomicMin(reinterpret_cast<long long *>(&A.err[1]), (long long)e);
+      }
+      if (cut) {                                                        // second pass
+        A.worklist[atomicAdd(A.wcount, 1)] = (int32_t)k;
+        continue;
+      }
+      if (dom != A.dt) {
+#pragma unroll 4
+        for (int t = 0; t < NE; t++) out[t] = 0.0;
+        if (A.npts) A.npts[k] = 0;
+        continue;
+      }
+    }
+    load_gc_thread<DIM, DORD>(A, e, v, gcs);
+    double acc[NT];
+#pragma unroll
+    for (int t = 0; t < NT; t++) acc[t] = 0.0;
+    double cm = A.form.c[0], cs = A.form.c[1], cn = A.form.c[2], cd = A.form.c[3];
+    double r2 = 0.0;
+#pragma unroll
+    for (int a = 0; a < DIM; a++) { double d = ls[a] - ls[DIM]; r2 += d * d; }
+    const bool iface = CUTPASS && A.dt == IF;
+    CutEntry E;
+    if (CUTPASS) E = A.tab->e[DIM - 2][A.dt][mask]; else { E.ns = 1; E.npt = 0; }
+    const double4 *rule = iface ? srule_if : srule_vol;
+    const int nr = iface ? A.nr_if : A.nr_vol;
+    bool first = true;
+    for (int s = 0; s < E.ns; s++) {
+      double P[4][3];
+      double sfac = 1.0;
+      if (CUTPASS) {
+        for (int a = 0; a < E.npt; a++) coded_point<DIM>(E.v[s][a], ls, P[a]);
+        sfac = simplex_factor(E.npt, P);
+      }
+      for (int q = 0; q < nr; q++) {
+        const double4 r = rule[q];
+        double xi[3] = {r.x, r.y, r.z};
+        if (CUTPASS) simplex_point(E.npt, P, r, xi);
+        double lam[4] = {xi[0], xi[1], xi[2], 0.0};
+        double last = 1.0;
+#pragma unroll
+        for (int a = 0; a < DIM; a++) last -= lam[a];
+        lam[DIM] = last;
+        double x[DIM], gl[DIM + 1][DIM], det;
+        iso_point<DIM, DORD>(GcThread<TT>{gcs}, lam, x, gl, det);
+        const double adet = fabs(det);
+        if (first) {
+          first = false;
+          if (hp) {                                                     // mesh_size at the first rule point of the element
+            const double h = DIM == 2 ? sqrt(adet) : cbrt(adet);
+            cm *= ipow(h, A.form.p[0]); cs *= ipow(h, A.form.p[1]); cn *= ipow(h, A.form.p[2]); cd *= ipow(h, A.form.p[3]);
+          }
+        }
+        double nrm[DIM], g2 = 0.0;
+#pragma unroll
+        for (int d = 0; d < DIM; d++) {
+          double t = 0.0;
+#pragma unroll
+          for (int a = 0; a <= DIM; a++) t += ls[a] * gl[a][d];
+          nrm[d] = t; g2 += t * t;
+        }
+        const double gn = sqrt(g2);
+        const double f = adet * (r.w * sfac * (iface ? gn / sqrt(r2) : 1.0));      // |det F| w |F^-T n_ref|
+        double S[ND], G[ND][DIM];
+#pragma unroll
+        for (int i = 0; i < ND; i++) h1_shape_grad<DIM, ORDER>(i, lam, gl, S[i], G[i]);
+        const double fs = f * cs, fm = f * cm;
+        if (!nterm) {
+          int t = 0;
+#pragma unroll
+          for (int i = 0; i < ND; i++) {
+            double gi[DIM];
+#pragma unroll
+            for (int d = 0; d < DIM; d++) gi[d] = fs * G[i][d];
+            const double si = fm * S[i];
+#pragma unroll
+            for (int j = 0; j <= i; j++) {
+              double a = acc[t];
+#pragma unroll
+              for (int d = 0; d < DIM; d++) a = fma(gi[d], G[j][d], a);
+              acc[t++] = fma(si, S[j], a);
+            }
+          }
+        } else {
+          const double inv = 1.0 / gn, fn = f * cn, fd = f * cd;
+          double DN[ND];
+#pragma unroll
+          for (int i = 0; i < ND; i++) {
+            double t = 0.0;
+#pragma unroll
+            for (int d = 0; d < DIM; d++) t += G[i][d] * nrm[d];
+            DN[i] = t * inv;
+          }
+          int t = 0;
+#pragma unroll
+          for (int i = 0; i < ND; i++) {
+            double gi[DIM];
+#pragma unroll
+            for (int d = 0; d < DIM; d++) gi[d] = fs * G[i][d];
+            const double si = fm * S[i] + fn * DN[i];                   // multiplies S_j
+            const double di = fn * S[i] + fd * DN[i];                   // multiplies DN_j
+#pragma unroll
+            for (int j = 0; j <= i; j++) {
+              double a = acc[t];
+#pragma unroll
+              for (int d = 0; d < DIM; d++) a = fma(gi[d], G[j][d], a);
+              a = fma(si, S[j], a);
+              acc[t++] = fma(di, DN[j], a);
+            }
+          }
+        }
+      }
+    }
+    {                                                                   // mirrored store of the symmetric block
+      int t = 0;
+#pragma unroll
+      for (int i = 0; i < ND; i++)
+#pragma unroll
+        for (int j = 0; j <= i; j++) {
+          out[i * ND + j] = acc[t];
+          if (j != i) out[j * ND + i] = acc[t];
+          t++;
+        }
+    }
+    if (A.npts) A.npts[k] = E.ns * nr;
+  }
+}
+
+// Integrate, thread per element: uncut elements of the domain and cut elements inline (1.5 % of a mesh), warp butterfly ->
+// partial[warp]; the shape of every partial sum depends on ne only
+template <int DIM, int DORD>
+__global__ void __launch_bounds__(TT) k_int_def_t(DefArgs A, int64_t ne) {
+  constexpr int NDG = H1<DIM, DORD>::ND;
+  extern __shared__ __align__(16) unsigned char smem_raw[];
+  double *gcs = reinterpret_cast<double *>(smem_raw) + threadIdx.x;
+  double4 *srule_vol = reinterpret_cast<double4 *>(smem_raw + (size_t)NDG * DIM * TT * 8);
+  double4 *srule_if = srule_vol + A.nr_vol;
+  for (int i = threadIdx.x; i < A.nr_vol; i += TT) srule_vol[i] = A.rule_vol[i];
+  for (int i = threadIdx.x; i < A.nr_if; i += TT) srule_if[i] = A.rule_if[i];
+  __syncthreads();
+  const int64_t nround = (ne + TT - 1) / TT;
+  for (int64_t b = blockIdx.x; b < nround; b += gridDim.x) {
+    const int64_t e = b * TT + threadIdx.x;
+    double sum = 0.0;
+    if (e < ne) {
+      int v[4];
+      load_vertices<DIM>(A.M, e, v);
+      double ls[4];
+#pragma unroll
+      for (int a = 0; a <= DIM; a++) ls[a] = __ldg(A.lset + v[a]);
+      int mask;
+      const int dom = sign_test<DIM>(ls, mask);
+      const bool cut = dom == IF;
+      if (cut || dom == A.dt) {
+        load_gc_thread<DIM, DORD>(A, e, v, gcs);
+        double r2 = 0.0;
+#pragma unroll
+        for (int a = 0; a < DIM; a++) { double d = ls[a] - ls[DIM]; r2 += d * d; }
+        const bool iface = cut && A.dt == IF;
+        CutEntry E;
+        if (cut) E = A.tab->e[DIM - 2][A.dt][mask]; else { E.ns = 1; E.npt = 0; }
+        const double4 *rule = iface ? srule_if : srule_vol;
+        const int nr = iface ? A.nr_if : A.nr_vol;
+        for (int s = 0; s < E.ns; s++) {
+          double P[4][3];
+          double sfac = 1.0;
+          if (cut) {
+            for (int a = 0; a < E.npt; a++) coded_point<DIM>(E.v[s][a], ls, P[a]);
+            sfac = simplex_factor(E.npt, P);
+          }
+          for (int q = 0; q < nr; q++) {
+            const double4 r = rule[q];
+            double xi[3] = {r.x, r.y, r.z};
+            if (cut) simplex_point(E.npt, P, r, xi);
+            double lam[4] = {xi[0], xi[1], xi[2], 0.0};
+            double last = 1.0;
+#pragma unroll
+            for (int a = 0; a < DIM; a++) last -= lam[a];
+            lam[DIM] = last;
+            double x[3] = {0.0, 0.0, 0.0}, gl[DIM + 1][DIM], det;
+            iso_point<DIM, DORD>(GcThread<TT>{gcs}, lam, x, gl, det);
+            double scale = 1.0;
+            if (iface) {
+              double g2 = 0.0;
+#pragma unroll
+              for (int d = 0; d < DIM; d++) {
+                double t = 0.0;
+#pragma unroll
+                for (int a = 0; a <= DIM; a++) t += ls[a] * gl[a][d];
+                g2 += t * t;
+              }
+              scale = sqrt(g2) / sqrt(r2);
+            }
+            double fv = 0.0;
+            for (int m = 0; m < A.f.n; m++)
+              fv += A.f.c[m] * ipow(x[0], A.f.ex[m][0]) * ipow(x[1], A.f.ex[m][1]) * ipow(x[2], A.f.ex[m][2]);
+            sum += fabs(det) * (r.w * sfac * scale) * fv;
+          }
+        }
+      }
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) sum += __shfl_xor_sync(0xffffffffu, sum, o);
+    if ((threadIdx.x & 31) == 0) A.partial[b * (TT / 32) + (threadIdx.x >> 5)] = sum;
   }
 }
 
@@ -366,26 +647,72 @@ static int grid_for(K kernel, size_t smem, int sm_count, int64_t nwarp_items, un
   return NGSX_OK;
 }
 
-template <int DIM, int ORDER, int DORD>
-static int launch_elmat_def(const DefArgs &A, int sm_count, int64_t nlist, cudaStream_t st) {
-  constexpr int ND = H1<DIM, ORDER>::ND, NDG = H1<DIM, DORD>::ND;
-  const size_t smem = DW * ((size_t)DQ * ND * 32 + (size_t)DQ * ND * 8 + DQ * 8 + NDG * DIM * 8);
-  auto kern = k_elmat_def<DIM, ORDER, DORD>;
-  unsigned grid;
-  if (int rc = grid_for(kern, smem, sm_count, nlist, &grid)) return rc;
-  kern<<<grid, DW * 32, smem, st>>>(A, nlist);
-  NGSX_LAUNCH_CHECK();
+template <typename K>
+static int grid_threads(K kernel, size_t smem, int sm_count, int64_t nitems, unsigned *grid) {
+  NGSX_CUDA(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  int occ = 0;
+  NGSX_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, kernel, TT, smem));
+  if (occ < 1) { set_error("kernel does not fit on an SM"); return NGSX_ERR_CUDA; }
+  *grid = (unsigned)std::max<int64_t>(1, std::min((nitems + TT - 1) / TT, (int64_t)sm_count * occ));
   return NGSX_OK;
 }
 
+static int g_def_warp = 0;      // debug switch: the first (warp-per-element) kernels
+
+template <int DIM, int ORDER, int DORD>
+static int launch_elmat_def(DefArgs &A, int sm_count, int64_t nlist, cudaStream_t st) {
+  constexpr int ND = H1<DIM, ORDER>::ND, NDG = H1<DIM, DORD>::ND;
+  if (g_def_warp) {
+    const size_t smem = DW * ((size_t)DQ * ND * 32 + (size_t)DQ * ND * 8 + DQ * 8 + NDG * DIM * 8);
+    auto kern = k_elmat_def<DIM, ORDER, DORD>;
+    unsigned grid;
+    if (int rc = grid_for(kern, smem, sm_count, nlist, &grid)) return rc;
+    kern<<<grid, DW * 32, smem, st>>>(A, nlist);
+    NGSX_LAUNCH_CHECK();
+    return NGSX_OK;
+  }
+  // pass 1: uncut elements (cut ones recorded), pass 2: the recorded cut elements
+  int32_t *work = nullptr;
+  NGSX_CUDA(cudaMallocAsync(&work, (nlist + 1) * sizeof(int32_t), st));
+  A.worklist = work + 1; A.wcount = work;
+  cudaError_t e0 = cudaMemsetAsync(work, 0, sizeof(int32_t), st);
+  const size_t smem = (size_t)NDG * DIM * TT * 8 + (size_t)(A.nr_vol + A.nr_if) * 32;
+  auto k1 = k_elmat_def_t<DIM, ORDER, DORD, false>;
+  auto k2 = k_elmat_def_t<DIM, ORDER, DORD, true>;
+  unsigned g1 = 1, g2 = 1;
+  int rc = grid_threads(k1, smem, sm_count, nlist, &g1);
+  if (!rc) rc = grid_threads(k2, smem, sm_count, nlist, &g2);
+  if (!rc) {
+    k1<<<g1, TT, smem, st>>>(A, nlist);
+    k2<<<g2, TT, smem, st>>>(A, nlist);
+    g_launches.fetch_add(2);
+  }
+  cudaError_t e1 = cudaGetLastError();
+  cudaFreeAsync(work, st);
+  if (rc) return rc;
+  NGSX_CUDA(e0);
+  NGSX_CUDA(e1);
+  return NGSX_OK;
+}
+
+// returns the number of partials through *npart
 template <int DIM, int DORD>
 static int launch_int_def(const DefArgs &A, int sm_count, int64_t ne, cudaStream_t st) {
   constexpr int NDG = H1<DIM, DORD>::ND;
-  const size_t smem = DW * (size_t)NDG * DIM * 8;
-  auto kern = k_int_def<DIM, DORD>;
+  if (g_def_warp) {
+    const size_t smem = DW * (size_t)NDG * DIM * 8;
+    auto kern = k_int_def<DIM, DORD>;
+    unsigned grid;
+    if (int rc = grid_for(kern, smem, sm_count, ne, &grid)) return rc;
+    kern<<<grid, DW * 32, smem, st>>>(A, ne);
+    NGSX_LAUNCH_CHECK();
+    return NGSX_OK;
+  }
+  const size_t smem = (size_t)NDG * DIM * TT * 8 + (size_t)(A.nr_vol + A.nr_if) * 32;
+  auto kern = k_int_def_t<DIM, DORD>;
   unsigned grid;
-  if (int rc = grid_for(kern, smem, sm_count, ne, &grid)) return rc;
-  kern<<<grid, DW * 32, smem, st>>>(A, ne);
+  if (int rc = grid_threads(kern, smem, sm_count, ne, &grid)) return rc;
+  kern<<<grid, TT, smem, st>>>(A, ne);
   NGSX_LAUNCH_CHECK();
   return NGSX_OK;
 }
@@ -415,6 +742,8 @@ static int check_common(const ngsx_mesh *mesh, const ngsx_deformation *defo, con
 }  // namespace ngsx
 
 using namespace ngsx;
+
+extern "C" void ngsx_debug_set_deformed_warp(int on) { g_def_warp = on; }
 
 extern "C" int ngsx_elmat_h1_deformed(const ngsx_mesh *mesh, const ngsx_deformation *defo, const double *lset_v, int fe_order, int dt,
                                       int intorder, const ngsx_form_h1 *h_form, int64_t nlist, const int32_t *els, double *elmats,
@@ -459,9 +788,10 @@ extern "C" int ngsx_integrate_deformed(const ngsx_mesh *mesh, const ngsx_deforma
   if (ne == 0) { NGSX_CUDA(cudaMemsetAsync(out, 0, sizeof(double), st)); return NGSX_OK; }
   A.f.n = h_f->nterms;
   for (int m = 0; m < A.f.n; m++) { A.f.c[m] = h_f->coef[m]; for (int d = 0; d < 3; d++) A.f.ex[m][d] = h_f->ex[m][d]; }
-  const unsigned nmid = (unsigned)std::min<int64_t>((ne + 255) / 256, 296);      // fixed upper bound: device-independent shape
+  const int64_t npart = g_def_warp ? ne : ((ne + TT - 1) / TT) * (TT / 32);      // one partial per element / per warp of 32 elements
+  const unsigned nmid = (unsigned)std::min<int64_t>((npart + 255) / 256, 296);   // fixed upper bound: device-independent shape
   double *partial = nullptr;
-  NGSX_CUDA(cudaMallocAsync(&partial, (ne + nmid) * sizeof(double), st));
+  NGSX_CUDA(cudaMallocAsync(&partial, (npart + nmid) * sizeof(double), st));
   A.partial = partial;
   int rc;
   switch (mesh->dim * 10 + defo->order) {
@@ -471,8 +801,8 @@ extern "C" int ngsx_integrate_deformed(const ngsx_mesh *mesh, const ngsx_deforma
     default: rc = launch_int_def<3, 2>(A, dd->sm_count, ne, st); break;
   }
   if (rc == NGSX_OK) {
-    k_def_reduce<<<nmid, 256, 0, st>>>(ne, partial, partial + ne);
-    k_def_reduce_final<<<1, 1024, 0, st>>>(nmid, partial + ne, out);
+    k_def_reduce<<<nmid, 256, 0, st>>>(npart, partial, partial + npart);
+    k_def_reduce_final<<<1, 1024, 0, st>>>(nmid, partial + npart, out);
     g_launches.fetch_add(2);
   }
   cudaError_t e1 = cudaGetLastError();

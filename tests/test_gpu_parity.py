@@ -893,8 +893,18 @@ def _deformed_setup(X, dim, dord, seed=3, amp=0.12):
 @pytest.mark.parametrize("dim", [2, 3])
 @pytest.mark.parametrize("fo", [1, 2])
 @pytest.mark.parametrize("dord", [1, 2])
-def test_deformed_elmats_against_oracle(X, dim, fo, dord):
+@pytest.mark.parametrize("warp", [0, 1])
+def test_deformed_elmats_against_oracle(X, dim, fo, dord, warp):
+    """warp = 0: thread-per-element passes (uncut, then the recorded cut elements); 1: the first warp-per-element kernel"""
     from oracle import orc
+    X.lib.load().ngsx_debug_set_deformed_warp(warp)
+    try:
+        _deformed_elmats(X, orc, dim, fo, dord)
+    finally:
+        X.lib.load().ngsx_debug_set_deformed_warp(0)
+
+
+def _deformed_elmats(X, orc, dim, fo, dord):
     mesh, gf, defo, Vd = _deformed_setup(X, dim, dord)
     mesh.SetDeformation(defo)
     Vh = X.ngs.H1(mesh, order=fo)

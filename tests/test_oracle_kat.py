@@ -158,3 +158,41 @@ def test_xfes_ndof():
     dom, _, nerr = orc.cutinfo_mesh(3, m.el2v.numpy(), m.vert.numpy(), ls)
     assert nerr == 0 and m.nv == 125
     assert orc.dofs_of_elements(m.el2v.numpy(), m.nv, dom == IF).sum() == 35
+
+
+# ---- deformed (isoparametric) meshes -------------------------------------------------------------
+@pytest.mark.parametrize("dim", [2, 3])
+@pytest.mark.parametrize("dord", [1, 2])
+def test_deformed_similarity_and_zero_deformation(dim, dord):
+    """closed forms for the oracle's isoparametric loops: a zero deformation reproduces the affine integrals; the similarity
+    d(x) = (s R - I) x scales volumes by s^dim and the interface by s^(dim-1) (per-point |F^-T n|, cutint/straightcutrule.cpp:558-576)"""
+    m = meshes.MakeStructured2DMesh(8) if dim == 2 else meshes.MakeStructured3DMesh(4)
+    vert, el2v = m.vert.numpy(), m.el2v.numpy()
+    ls = p1((lambda x, y: np.sqrt((x - .5) ** 2 + (y - .5) ** 2) - 0.33) if dim == 2 else
+            (lambda x, y, z: np.sqrt((x - .5) ** 2 + (y - .5) ** 2 + (z - .5) ** 2) - 0.33), vert)
+    e2d, ndof = m.h1_dofs(dord)
+    e2d = e2d.numpy()
+    s, th = 1.7, 0.4
+    R = np.eye(dim)
+    R[0, 0], R[0, 1], R[1, 0], R[1, 1] = np.cos(th), -np.sin(th), np.sin(th), np.cos(th)
+    zero = np.zeros((ndof, dim))
+    sim = zero.copy()
+    sim[:m.nv] = vert @ (s * R - np.eye(dim)).T
+    mono = [(1.0, 0, 0, 0)]
+    for dt in (NEG, POS, IF):
+        base = integrate(m, ls, dt, 2)
+        z = orc.integrate_mesh_iso(dim, el2v, vert, ls, dord, e2d, zero, dt, 2, mono)[0]
+        g = orc.integrate_mesh_iso(dim, el2v, vert, ls, dord, e2d, sim, dt, 2, mono)[0]
+        assert abs(z - base) <= 1e-13 * abs(base)
+        assert abs(g - base * (s ** dim if dt != IF else s ** (dim - 1))) <= 1e-12 * abs(g)
+    # a curved (order-2) boundary-preserving deformation keeps NEG + POS = |Omega| = 1
+    if dord == 2:
+        rng = np.random.default_rng(5)
+        bub = zero.copy()
+        e2v, _ = m.edges()
+        e2v = e2v.numpy()
+        on_bnd = lambda p: np.any((np.abs(p) < 1e-12) | (np.abs(p - 1) < 1e-12), axis=1)
+        inner_edge = ~(on_bnd(vert[e2v[:, 0]]) & on_bnd(vert[e2v[:, 1]]))
+        bub[m.nv:][inner_edge] = 0.05 * rng.uniform(-1, 1, (int(inner_edge.sum()), dim))
+        tot = sum(orc.integrate_mesh_iso(dim, el2v, vert, ls, dord, e2d, bub, dt, 4, mono)[0] for dt in (NEG, POS))
+        assert abs(tot - 1.0) <= 1e-12
