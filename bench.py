@@ -129,7 +129,12 @@ def build_problem(nx, device, rank=0, world=1, group=6):
                           definedonelements=restr)
     mesh_int = mesh                                      # this rank's elements of CutInfo.Update and the Integrate() reductions
     if world > 1:
-        mesh_int = mesh.element_block(*partition.element_block(mesh.ne, rank, world))
+        wcut = float(os.environ.get("NGSX_BENCH_SWEEP_CUTWEIGHT", "40"))             # sweeps: a cut element ~ 40 sign tests (0: equal counts)
+        if wcut > 0:
+            blocks = partition.element_blocks_weighted(1.0 + wcut * (ci.dom == xfem.IF).to(torch.float64), world)
+            mesh_int = mesh.element_block(*blocks[rank])
+        else:
+            mesh_int = mesh.element_block(*partition.element_block(mesh.ne, rank, world))
         ci = xfem.CutInfo(mesh_int, lsetp1)
     return dict(mesh=mesh, mesh_int=mesh_int, lsetp1=lsetp1, ci=ci, Vh=Vh, a=a, n_total=n_total, xfem=xfem)
 
@@ -151,7 +156,9 @@ def run_b200(args):
     from ngsxfem_b200 import _lib
     L = _lib.load()
     t0 = time.time()
-    P = build_problem(args.nx, dev, rank, world, args.group)
+    emu = os.environ.get("NGSX_BENCH_EMULATE")           # "r/N": rank r's share of an N-GPU run on this one GPU (no collective), for tuning
+    prank, pworld = (int(t) for t in emu.split("/")) if emu else (rank, world)
+    P = build_problem(args.nx, dev, prank, pworld, args.group)
     mesh, lsetp1, ci, a, xfem, mesh_int = P["mesh"], P["lsetp1"], P["ci"], P["a"], P["xfem"], P["mesh_int"]
     a.Assemble()                                         # symbolic phase (graph, colouring, slot map) + first numeric pass
     torch.cuda.synchronize()
@@ -164,18 +171,20 @@ def run_b200(args):
     ev = lambda: torch.cuda.Event(enable_timing=True)
     stage_ms = {"classify": [], "assemble": [], "integrate": []}
 
-    # classification and the two Integrate() calls depend on the level set only.  At N = 1 they are issued on three streams
-    # behind the assembly chain: the latency-bound sweeps and cut passes overlap each other (0.40 -> 0.34 ms), the row gather
-    # keeps the machine to itself (1.33 -> 1.25 ms per step).  Issued together with the assembly the step is 1.22 ms, but the
-    # row gather then shares its SMs (0.70 -> 0.79 ms) -- NGSX_BENCH_ORDER=with.  At N > 1 every kernel is short and the extra
-    # stream bookkeeping on the host costs more than the overlap gains (measured at N = 4: 0.50 ms serial, 0.57 ms on four
-    # streams), so the ranks of a multi-GPU run keep one stream.
+    # classification and the two Integrate() calls depend on the level set only: they run on three side streams.  History of the
+    # order at N = 1: behind the assembly chain 1.25 ms ("after"; the sweeps overlap each other, 0.40 -> 0.34 ms); beside the whole
+    # chain 1.22 ms ("with"; the row gather then shares its SMs, 0.70 -> 0.79 ms); beside k_geom + k_cutmat with the gather waiting
+    # for them ("join", the default) the sweeps hide behind the small kernels and the gather keeps the machine to itself.
     main = torch.cuda.current_stream()
     side = [torch.cuda.Stream() for _ in range(3)]
-    serial = world > 1 or bool(os.environ.get("NGSX_BENCH_SERIAL"))      # NGSX_BENCH_SERIAL: A/B switch at N = 1
-    after_asm = os.environ.get("NGSX_BENCH_ORDER", "after") == "after"   # the three sweeps overlap each other, not the row gather
+    serial = pworld > 1 or bool(os.environ.get("NGSX_BENCH_SERIAL"))      # NGSX_BENCH_SERIAL: A/B switch at N = 1
+    # order of the three sweeps relative to the assembly chain (k_geom -> k_cutmat -> k_rows):
+    #   "join"  (default): the sweeps start with the chain, and the row gather waits for them (ngsx_set_gather_wait_event): the
+    #            latency-bound sweeps share the machine with the small geometry / quadrature kernels, the gather runs alone;
+    #   "after": the sweeps start when the whole chain is done;  "with": they start with the chain, the gather does not wait.
+    order_default = os.environ.get("NGSX_BENCH_ORDER", "join")
 
-    def step(record, serial=serial, timing=True, order_after=after_asm):
+    def step(record, serial=serial, timing=True, order=order_default):
         mk = ev if timing else (lambda: torch.cuda.Event())              # no timing events inside a graph capture
         e = [mk() for _ in range(6)]
         cur = torch.cuda.current_stream()
@@ -186,15 +195,30 @@ def run_b200(args):
             s_if = xfem.IntegrateX(lsetp1, mesh_int, cf=1.0, order=4, domain_type=xfem.IF, sync=False); e[3].record()
             s_neg = xfem.IntegrateX(lsetp1, mesh_int, cf=1.0, order=4, domain_type=xfem.NEG, sync=False); e[4].record()
         else:
-            a.Assemble(); e[2].record()                                  # the assembly chain alone on the main stream
-            for st in side:
-                st.wait_event(e[2] if order_after else e[0])
-            with torch.cuda.stream(side[0]):
-                ci.Update(lsetp1); e[1].record()
-            with torch.cuda.stream(side[1]):
-                s_if = xfem.IntegrateX(lsetp1, mesh_int, cf=1.0, order=4, domain_type=xfem.IF, sync=False); e[3].record()
-            with torch.cuda.stream(side[2]):
-                s_neg = xfem.IntegrateX(lsetp1, mesh_int, cf=1.0, order=4, domain_type=xfem.NEG, sync=False); e[4].record()
+            def sweeps():
+                with torch.cuda.stream(side[0]):
+                    ci.Update(lsetp1); e[1].record()
+                with torch.cuda.stream(side[1]):
+                    r_if = xfem.IntegrateX(lsetp1, mesh_int, cf=1.0, order=4, domain_type=xfem.IF, sync=False); e[3].record()
+                with torch.cuda.stream(side[2]):
+                    r_neg = xfem.IntegrateX(lsetp1, mesh_int, cf=1.0, order=4, domain_type=xfem.NEG, sync=False); e[4].record()
+                return r_if, r_neg
+            if order == "after":
+                a.Assemble(); e[2].record()                              # the assembly chain alone on the main stream
+                for st in side:
+                    st.wait_event(e[2])
+                s_if, s_neg = sweeps()
+            else:
+                for st in side:
+                    st.wait_event(e[0])
+                s_if, s_neg = sweeps()
+                if order == "join":
+                    side[0].wait_event(e[3]); side[0].wait_event(e[4])
+                    joined = torch.cuda.Event()
+                    joined.record(side[0])
+                    a.Assemble(gather_after=joined); e[2].record()
+                else:
+                    a.Assemble(); e[2].record()
             for st in side:
                 cur.wait_stream(st)
             s_if.record_stream(cur); s_neg.record_stream(cur)
@@ -209,7 +233,7 @@ def run_b200(args):
     # and the library's per-kernel timing events for the roofline cannot be recorded inside a graph.)
     graph, g_out, graph_note = None, None, "eager"
     comm = torch.cuda.Stream() if (world > 1 and not os.environ.get("NGSX_BENCH_NOCOMMSTREAM")) else None
-    if world > 1 and not os.environ.get("NGSX_BENCH_NOGRAPH"):
+    if (pworld > 1 or os.environ.get("NGSX_BENCH_GRAPH")) and not os.environ.get("NGSX_BENCH_NOGRAPH"):
         try:
             ref_if, ref_neg = step(None)
             ref_vals = a.mat.vals.clone()
@@ -217,7 +241,7 @@ def run_b200(args):
             graph = torch.cuda.CUDAGraph()
             lps0 = L.ngsx_launch_count()
             with torch.cuda.graph(graph):
-                g_out = step(None, serial=False, timing=False, order_after=os.environ.get("NGSX_BENCH_ORDER", "with") == "after")
+                g_out = step(None, serial=False, timing=False)
             launches_per_replay = L.ngsx_launch_count() - lps0           # kernel nodes of this library in the graph
             a.mat.vals.fill_(float("nan"))
             graph.replay()
@@ -229,7 +253,7 @@ def run_b200(args):
                 raise RuntimeError(f"graph replay differs from the eager step {chk} {int(wrote.sum())} {plan.nnz_covered}")
             a.mat.vals.copy_(ref_vals)
             del wrote
-            graph_note = "CUDA graph per rank (assembly chain + three forked sweep streams), NCCL all-reduce outside"
+            graph_note = f"CUDA graph per rank (assembly chain + three forked sweep streams, order '{order_default}'), NCCL all-reduce outside"
             del ref_vals
         except Exception as exc:                                         # capture unsupported on this driver: stay eager
             graph, graph_note = None, f"eager (graph capture failed: {type(exc).__name__}: {str(exc)[:200]})"
@@ -285,7 +309,7 @@ def run_b200(args):
     L.ngsx_debug_set_timing(0)
     total_ms = t_begin.elapsed_time(t_end)
     for e in rec:                                        # per stage: from its start event to its last kernel, on its stream
-        t0s = e[0] if (serial or not after_asm) else e[2]                    # the sweeps start when the assembly chain ends
+        t0s = e[2] if (not serial and order_default == "after") else e[0]   # "after": the sweeps start when the assembly chain ends
         stage_ms["classify"].append(e[0].elapsed_time(e[1]) if serial else t0s.elapsed_time(e[1]))
         stage_ms["assemble"].append(e[1].elapsed_time(e[2]) if serial else e[0].elapsed_time(e[2]))
         stage_ms["integrate"].append(e[2].elapsed_time(e[4]) if serial else max(t0s.elapsed_time(e[3]), t0s.elapsed_time(e[4])))
@@ -423,7 +447,9 @@ def run_b200(args):
                    "ne": mesh.ne, "hasneg_elements": n_global, "nnz": nnz_global, "assembly": a.assembly, "group": args.group, "colors": plan.ncolors,
                    "setup_s_untimed": round(setup_s, 2), "stage_ms": {"classify": cl_ms, "assemble": as_ms, "integrate": in_ms},
                    "stage_ms_one_stream": serial_break, "launch": graph_note,
-                   "streams": "1 (serial stages)" if serial else "assemble, then CutInfo.Update | Integrate(IF) | Integrate(NEG) on three streams; stage_ms = stage start to its last kernel (the three sweeps overlap)",
+                   "streams": "1 (serial stages)" if serial else {"join": "CutInfo.Update | Integrate(IF) | Integrate(NEG) on three streams beside k_geom + k_cutmat; the row gather waits for them (ngsx_set_gather_wait_event) and runs alone; stage_ms = step start to the stage's last kernel, 'assemble' therefore contains the wait",
+                                                                     "after": "assemble, then CutInfo.Update | Integrate(IF) | Integrate(NEG) on three streams; stage_ms = stage start to its last kernel (the three sweeps overlap)",
+                                                                     "with": "the three sweeps on three streams beside the whole assembly chain"}[order_default],
                    "l2": "inputs larger than L2 (CSR values + pair descriptors + mesh > 1.4 GB touched per step vs 126 MB L2); no explicit flush",
                    "partition": "owner-computes: contiguous chunks of equal cost (cut element = 3.2 uncut) of the HASNEG element list per rank, a CSR row belongs to the rank of the first listed element touching it, halo elements re-evaluated, no interface-row exchange; element blocks for Integrate, scalars all-reduced (NCCL)"},
         "roofline": {"bound": "hbm", "kernel": "k_rows<10,6> (owner-computes row gather: every CSR value of the assembled operator written once)",

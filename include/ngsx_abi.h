@@ -199,6 +199,12 @@ int ngsx_assemble_csr_rows_h1(const ngsx_mesh *mesh, const double *lset_v, int f
                               const ngsx_form_h1 *h_form, int64_t nlist, const int32_t *els, ngsx_rowplan *plan,
                               int accumulate, double *vals, int64_t *err, void *stream);
 
+/* One-shot ordering hint for the NEXT ngsx_assemble_csr_rows_h1 call of this host thread: its stream waits for `event` (a
+ * cudaEvent_t the caller recorded on another stream; NULL clears) after the cut-element stage and before the row gather.  The
+ * gather is the one kernel that fills the machine; a caller with independent latency-bound work on side streams (CutInfo.Update,
+ * Integrate: NGS task-parallel regions in the reference) overlaps it with the geometry / quadrature stage and keeps the
+ * gather alone on the SMs.  Capturable (the wait becomes a graph edge). */
+void ngsx_set_gather_wait_event(void *event);
 /* General form of AddElementMatrix (NGS/linalg/sparsematrix_impl.hpp:63-103) over a plan: mats [nlist][nd][nd] row-major
  * blocks of the plan's list entries (elements, or facet patches with their merged dof lists) are gathered row by row;
  * accumulate as above.  nd in {3, 4, 5, 6, 8, 9, 10, 12, 14, 20}. */

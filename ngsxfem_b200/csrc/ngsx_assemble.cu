@@ -1028,6 +1028,7 @@ static cudaEvent_t g_evr[TIMING_RING][4];
 static cudaEvent_t *g_ev = g_evr[0];
 static int g_ev_calls = 0;      // timed calls since the last ngsx_debug_get_timing
 static bool g_ev_ready = false;
+static thread_local cudaEvent_t g_gather_wait = nullptr;      // one-shot: see ngsx_set_gather_wait_event
 
 }  // namespace ngsx
 
@@ -1105,9 +1106,13 @@ int ngsx_assemble_csr_h1(const ngsx_mesh *mesh, const double *lset_v, int fe_ord
   return dispatch_elmat<1>(A, fe_order, dd->sm_count, ncolors, h_color_ptr, nlist, as_stream(stream));
 }
 
+void ngsx_set_gather_wait_event(void *event) { g_gather_wait = reinterpret_cast<cudaEvent_t>(event); }
+
 int ngsx_assemble_csr_rows_h1(const ngsx_mesh *mesh, const double *lset_v, int fe_order, int dt, int intorder,
                               const ngsx_form_h1 *h_form, int64_t nlist, const int32_t *els, ngsx_rowplan *plan,
                               int accumulate, double *vals, int64_t *err, void *stream) {
+  cudaEvent_t gather_wait = g_gather_wait;
+  g_gather_wait = nullptr;
   const DeviceData *dd; const double4 *rv, *ri; int nv, ni;
   NGSX_REQUIRE(h_form && plan && nlist >= 0 && nlist == plan->nlist, "assemble_csr_rows_h1: bad arguments (nlist must match the plan)");
   NGSX_REQUIRE(plan->nrows == 0 || vals, "assemble_csr_rows_h1: vals is NULL");
@@ -1149,6 +1154,7 @@ int ngsx_assemble_csr_rows_h1(const ngsx_mesh *mesh, const double *lset_v, int f
   A.elmats = plan->cutmats; A.npts = nullptr;
   // the work-list length lives on the device: launch the persistent grid for the worst case, idle CTAs leave at once
   if (int rc = launch_cutmat(A, fe_order, dd->sm_count, nlist, st)) return rc;
+  if (gather_wait) NGSX_CUDA(cudaStreamWaitEvent(st, gather_wait, 0));      // the gather starts once the caller's side work is done
   if (g_timing) cudaEventRecord(g_ev[2], st);
   const int rc = launch_rows(plan, npairtab, accumulate, vals, dd->sm_count, st);
   if (g_timing) cudaEventRecord(g_ev[3], st);

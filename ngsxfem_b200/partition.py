@@ -41,6 +41,20 @@ def element_block(ne: int, rank: int, world: int) -> Tuple[int, int]:
     return (ne * rank) // world, (ne * (rank + 1)) // world
 
 
+def element_blocks_weighted(weights: torch.Tensor, world: int) -> List[Tuple[int, int]]:
+    """contiguous element blocks [lo, hi) tiling [0, ne) with ~equal total weight (element-wise sweeps: a cut element costs
+    tens of uncut ones -- cut ratio / cut integral against a sign test -- and the cut elements of a sphere crowd the middle slabs)"""
+    ne = weights.numel()
+    csum = torch.cumsum(weights.to(torch.float64), 0)
+    total = float(csum[-1].item()) if ne else 0.0
+    bounds = [0]
+    for r in range(1, world):
+        b = int(torch.searchsorted(csum, torch.tensor(total * r / world, device=csum.device, dtype=csum.dtype)).item())
+        bounds.append(max(bounds[-1], min(b, ne)))
+    bounds.append(ne)
+    return [(bounds[r], bounds[r + 1]) for r in range(world)]
+
+
 def row_owners(el2dof_active: torch.Tensor, ndof: int, world: int, weights: torch.Tensor = None) -> torch.Tensor:
     """owner[dof] = rank whose chunk of the active list holds the first element touching the dof; -1: untouched.  int32 [ndof].
     The list is cut into `world` contiguous chunks of equal element count, or of equal total weight when per-element cost

@@ -673,8 +673,10 @@ class BilinearForm:
         plan.mats = torch.empty((npatch, ndp * ndp), dtype=torch.float64, device=mesh.device)
         return plan
 
-    def Assemble(self, reallocate: bool = False):
-        """S_BilinearForm::DoAssemble (NGS/comp/bilinearform.cpp:929-1575): SetZero, then every integrator colour by colour"""
+    def Assemble(self, reallocate: bool = False, gather_after=None):
+        """S_BilinearForm::DoAssemble (NGS/comp/bilinearform.cpp:929-1575): SetZero, then every integrator colour by colour.
+        gather_after: a recorded torch.cuda.Event of a side stream -- the row gather of the (first) H1 row-plan integrator starts
+        only after it (ngsx_set_gather_wait_event), the geometry / quadrature stage before it overlaps the side work"""
         L = _lib_()
         fes = self.space
         if self.mat is None or reallocate:
@@ -719,6 +721,9 @@ class BilinearForm:
                 check(L.ngsx_assemble_csr_rows_mats(plan.handle, _ptr(plan.mats), 0 if overwrite else 1, _ptr(self.mat.vals), _stream()))
             elif isinstance(plan, _RowPlan):
                 lv = _lset_vec(integ.lset)
+                if gather_after is not None:
+                    L.ngsx_set_gather_wait_event(ctypes.c_void_p(gather_after.cuda_event))
+                    gather_after = None
                 check(L.ngsx_assemble_csr_rows_h1(mesh_c, _ptr(lv), fes.order, integ.dt, integ.intorder(fes.order), ctypes.byref(integ.form),
                                                   plan.els.numel(), _ptr(plan.els), plan.handle, 0 if overwrite else 1,
                                                   _ptr(self.mat.vals), _ptr(self._err[k]), _stream()))

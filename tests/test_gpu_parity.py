@@ -1043,3 +1043,33 @@ def test_deformed_unsupported_paths_raise(X):
     with pytest.raises(X.lib.NgsxError):
         f.Assemble()
     mesh.UnsetDeformation()
+
+
+def test_gather_wait_event_orders_only(X):
+    """ngsx_set_gather_wait_event: the row gather waits for a side-stream event; values are bitwise those of the plain call and
+    the hint is one-shot"""
+    mesh = X.ngs.Mesh(X.meshes.MakeStructured3DMesh(8))
+    gf = X.ngs.GridFunction(X.ngs.H1(mesh, order=1))
+    X.xfem.InterpolateToP1(X.ngs.SphereLevelset((0.5, 0.5, 0.5), 0.35), gf)
+    Vh = X.ngs.H1(mesh, order=2)
+    u, v = Vh.TnT()
+    a = X.xfem.BilinearForm(Vh)
+    a += X.xfem.SymbolicBFI(levelset_domain={"levelset": gf, "domain_type": NEG}, form=X.ngs.grad(u) * X.ngs.grad(v) + u * v)
+    a.Assemble()
+    ref = a.mat.vals.clone()
+    side = torch.cuda.Stream()
+    main = torch.cuda.current_stream()
+    for _ in range(3):
+        a.mat.vals.fill_(float("nan"))
+        side.wait_stream(main)
+        with torch.cuda.stream(side):
+            s = X.xfem.IntegrateX(gf, mesh, cf=1.0, order=4, domain_type=IF, sync=False)
+            evt = torch.cuda.Event()
+            evt.record()
+        a.Assemble(gather_after=evt)
+        main.wait_stream(side)
+        torch.cuda.synchronize()
+        assert torch.equal(a.mat.vals, ref)
+        a.Assemble()                                                              # one-shot: no stale event on the next call
+        assert torch.equal(a.mat.vals, ref)
+    assert abs(float(s.item()) - 4 * np.pi * 0.35 ** 2) < 0.1
