@@ -147,6 +147,7 @@ def run_b200(args):
     torch.cuda.set_device(lrank)
     dev = f"cuda:{lrank}"
     if world > 1:
+        os.environ.setdefault("NCCL_DEBUG_FILE", "/dev/stderr")        # NCCL's version / debug lines must not land beside the JSON line on stdout
         dist.init_process_group("nccl", device_id=torch.device(dev))
     import __graft_entry__ as ge
     if rank == 0:
