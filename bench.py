@@ -457,6 +457,9 @@ def run_b200(args):
                      "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": traffic,
                      "peak_source": peak_src, "algorithmic_bytes_per_element": ALGO_BYTES_SCATTER,
                      "kernel_ms": {"k_geom": geom_ms, "k_cutmat": cut_ms, "k_rows": rows_ms},
+                     "kernel_ms_note": ("live in the timed region; with the sweeps beside them k_geom / k_cutmat share the SMs and the k_cutmat interval "
+                                        "ends after the gather's wait for the sweeps (config.stage_ms_one_stream.kernel_ms has them alone); k_rows runs alone")
+                                       if (not serial and order_default == "join") else "live in the timed region",
                      "assemble_stage": {"achieved": stage_achieved, "frac": stage_achieved / peak, "algorithmic_bytes_per_element": ALGO_BYTES_PER_ELEMENT},
                      "own_algorithm": None if own_bytes is None else {"bytes_per_launch": own_bytes, "achieved": own_bytes / (rows_ms * 1e-3) / 1e9,
                                                                     "frac": own_bytes / (rows_ms * 1e-3) / 1e9 / peak,
