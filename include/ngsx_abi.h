@@ -240,6 +240,11 @@ typedef struct ngsx_deformation {
 int ngsx_elmat_h1_deformed(const ngsx_mesh *mesh, const ngsx_deformation *defo, const double *lset_v, int fe_order, int dt, int intorder,
                            const ngsx_form_h1 *h_form, int64_t nlist, const int32_t *els, double *elmats, int32_t *npts,
                            int64_t *err, void *stream);
+/* batched CalcElementVector (xfem/symboliccutlfi.cpp:52-158) on the deformed mesh, f evaluated at the mapped points; arguments as
+ * ngsx_elvec_h1.  The dense vectors reach the global vector through ngsx_gather_vec (fixed order, no atomics). */
+int ngsx_elvec_h1_deformed(const ngsx_mesh *mesh, const ngsx_deformation *defo, const double *lset_v, int fe_order, int dt, int intorder,
+                           const ngsx_poly *h_f, int64_t nlist, const int32_t *els, double *elvecs, int32_t *npts,
+                           int64_t *err, void *stream);
 /* IntegrateX (cutint/python_cutint.cpp:20-72) on the deformed mesh: f is evaluated at the mapped points */
 int ngsx_integrate_deformed(const ngsx_mesh *mesh, const ngsx_deformation *defo, const double *lset_v, int dt, int order,
                             const ngsx_poly *h_f, double *out, void *stream);

@@ -515,17 +515,104 @@ __global__ void __launch_bounds__(TT) k_elmat_def_t(DefArgs A, int64_t count) {
       }
     }
     {                                                                   // mirrored store of the symmetric block
-      int t = 0;
+      auto tri = [](int i, int j) { return i >= j ? i * (i + 1) / 2 + j : j * (j + 1) / 2 + i; };
+      if constexpr (NE % 2 == 0) {                                      // 16-byte stores: the block starts 16-byte aligned (NE even)
+        double2 *o2 = reinterpret_cast<double2 *>(out);
 #pragma unroll
-      for (int i = 0; i < ND; i++)
+        for (int t = 0; t < NE / 2; t++)
+          o2[t] = make_double2(acc[tri((2 * t) / ND, (2 * t) % ND)], acc[tri((2 * t + 1) / ND, (2 * t + 1) % ND)]);
+      } else {
 #pragma unroll
-        for (int j = 0; j <= i; j++) {
-          out[i * ND + j] = acc[t];
-          if (j != i) out[j * ND + i] = acc[t];
-          t++;
-        }
+        for (int t = 0; t < NE; t++) out[t] = acc[tri(t / ND, t % ND)];
+      }
     }
     if (A.npts) A.npts[k] = E.ns * nr;
+  }
+}
+
+// element vectors (SymbolicCutLFI on a deformed mesh, xfem/symboliccutlfi.cpp:52-158): thread per element, cut elements inline
+// (per point only the ND shape values and the integrand at the mapped point: the quadrature is a small part of the work)
+template <int DIM, int ORDER, int DORD>
+__global__ void __launch_bounds__(TT) k_elvec_def_t(DefArgs A, int64_t count) {
+  constexpr int ND = H1<DIM, ORDER>::ND, NDG = H1<DIM, DORD>::ND;
+  extern __shared__ __align__(16) unsigned char smem_raw[];
+  double *gcs = reinterpret_cast<double *>(smem_raw) + threadIdx.x;
+  double4 *srule_vol = reinterpret_cast<double4 *>(smem_raw + (size_t)NDG * DIM * TT * 8);
+  double4 *srule_if = srule_vol + A.nr_vol;
+  for (int i = threadIdx.x; i < A.nr_vol; i += TT) srule_vol[i] = A.rule_vol[i];
+  for (int i = threadIdx.x; i < A.nr_if; i += TT) srule_if[i] = A.rule_if[i];
+  __syncthreads();
+  for (int64_t k = (int64_t)blockIdx.x * TT + threadIdx.x; k < count; k += (int64_t)gridDim.x * TT) {
+    const int64_t e = A.els ? A.els[k] : k;
+    int v[4];
+    load_vertices<DIM>(A.M, e, v);
+    double ls[4];
+#pragma unroll
+    for (int a = 0; a <= DIM; a++) ls[a] = __ldg(A.lset + v[a]);
+    int mask;
+    const int dom = sign_test<DIM>(ls, mask);
+    const bool cut = dom == IF;
+    if (dom < 0 && A.err) {
+      atomicAdd(&A.err[0], 1ULL);
+      atomicMin(reinterpret_cast<long long *>(&A.err[1]), (long long)e);
+    }
+    double acc[ND];
+#pragma unroll
+    for (int i = 0; i < ND; i++) acc[i] = 0.0;
+    int np_used = 0;
+    if (cut || dom == A.dt) {
+      load_gc_thread<DIM, DORD>(A, e, v, gcs);
+      double r2 = 0.0;
+#pragma unroll
+      for (int a = 0; a < DIM; a++) { double d = ls[a] - ls[DIM]; r2 += d * d; }
+      const bool iface = cut && A.dt == IF;
+      CutEntry E;
+      if (cut) E = A.tab->e[DIM - 2][A.dt][mask]; else { E.ns = 1; E.npt = 0; }
+      const double4 *rule = iface ? srule_if : srule_vol;
+      const int nr = iface ? A.nr_if : A.nr_vol;
+      np_used = E.ns * nr;
+      for (int s = 0; s < E.ns; s++) {
+        double P[4][3];
+        double sfac = 1.0;
+        if (cut) {
+          for (int a = 0; a < E.npt; a++) coded_point<DIM>(E.v[s][a], ls, P[a]);
+          sfac = simplex_factor(E.npt, P);
+        }
+        for (int q = 0; q < nr; q++) {
+          const double4 r = rule[q];
+          double xi[3] = {r.x, r.y, r.z};
+          if (cut) simplex_point(E.npt, P, r, xi);
+          double lam[4] = {xi[0], xi[1], xi[2], 0.0};
+          double last = 1.0;
+#pragma unroll
+          for (int a = 0; a < DIM; a++) last -= lam[a];
+          lam[DIM] = last;
+          double x[3] = {0.0, 0.0, 0.0}, gl[DIM + 1][DIM], det;
+          iso_point<DIM, DORD>(GcThread<TT>{gcs}, lam, x, gl, det);
+          double scale = 1.0;
+          if (iface) {
+            double g2 = 0.0;
+#pragma unroll
+            for (int d = 0; d < DIM; d++) {
+              double t = 0.0;
+#pragma unroll
+              for (int a = 0; a <= DIM; a++) t += ls[a] * gl[a][d];
+              g2 += t * t;
+            }
+            scale = sqrt(g2) / sqrt(r2);
+          }
+          double fv = 0.0;
+          for (int m = 0; m < A.f.n; m++)
+            fv += A.f.c[m] * ipow(x[0], A.f.ex[m][0]) * ipow(x[1], A.f.ex[m][1]) * ipow(x[2], A.f.ex[m][2]);
+          const double pv = fabs(det) * (r.w * sfac * scale) * fv;
+#pragma unroll
+          for (int i = 0; i < ND; i++) acc[i] += pv * h1_shape<DIM, ORDER>(i, lam);
+        }
+      }
+    }
+#pragma unroll
+    for (int i = 0; i < ND; i++) A.elmats[k * ND + i] = acc[i];
+    if (A.npts) A.npts[k] = np_used;
   }
 }
 
@@ -695,6 +782,18 @@ static int launch_elmat_def(DefArgs &A, int sm_count, int64_t nlist, cudaStream_
   return NGSX_OK;
 }
 
+template <int DIM, int ORDER, int DORD>
+static int launch_elvec_def(const DefArgs &A, int sm_count, int64_t nlist, cudaStream_t st) {
+  constexpr int NDG = H1<DIM, DORD>::ND;
+  const size_t smem = (size_t)NDG * DIM * TT * 8 + (size_t)(A.nr_vol + A.nr_if) * 32;
+  auto kern = k_elvec_def_t<DIM, ORDER, DORD>;
+  unsigned grid;
+  if (int rc = grid_threads(kern, smem, sm_count, nlist, &grid)) return rc;
+  kern<<<grid, TT, smem, st>>>(A, nlist);
+  NGSX_LAUNCH_CHECK();
+  return NGSX_OK;
+}
+
 // returns the number of partials through *npart
 template <int DIM, int DORD>
 static int launch_int_def(const DefArgs &A, int sm_count, int64_t ne, cudaStream_t st) {
@@ -771,6 +870,38 @@ extern "C" int ngsx_elmat_h1_deformed(const ngsx_mesh *mesh, const ngsx_deformat
     case 312: return launch_elmat_def<3, 1, 2>(A, dd->sm_count, nlist, st);
     case 321: return launch_elmat_def<3, 2, 1>(A, dd->sm_count, nlist, st);
     case 322: return launch_elmat_def<3, 2, 2>(A, dd->sm_count, nlist, st);
+  }
+  set_error("unsupported (dim, order, deformation order)");
+  return NGSX_ERR_UNSUPPORTED;
+}
+
+extern "C" int ngsx_elvec_h1_deformed(const ngsx_mesh *mesh, const ngsx_deformation *defo, const double *lset_v, int fe_order, int dt,
+                                      int intorder, const ngsx_poly *h_f, int64_t nlist, const int32_t *els, double *elvecs,
+                                      int32_t *npts, int64_t *err, void *stream) {
+  NGSX_REQUIRE(h_f && (nlist == 0 || elvecs) && nlist >= 0, "elvec_h1_deformed: bad arguments");
+  NGSX_REQUIRE(h_f->nterms >= 0 && h_f->nterms <= NGSX_POLY_MAXTERMS, "elvec_h1_deformed: too many polynomial terms");
+  if (fe_order < 1 || fe_order > 2) {
+    set_error("H1 order outside the CUDA path (supported: 1, 2); no CPU fallback");
+    return NGSX_ERR_UNSUPPORTED;
+  }
+  const DeviceData *dd;
+  DefArgs A{};
+  if (int rc = check_common(mesh, defo, lset_v, dt, intorder, &dd, A)) return rc;
+  cudaStream_t st = as_stream(stream);
+  if (err) { if (int rc = reset_err(err, st)) return rc; }
+  if (nlist == 0) return NGSX_OK;
+  A.f.n = h_f->nterms;
+  for (int m = 0; m < A.f.n; m++) { A.f.c[m] = h_f->coef[m]; for (int d = 0; d < 3; d++) A.f.ex[m][d] = h_f->ex[m][d]; }
+  A.els = els; A.elmats = elvecs; A.npts = npts; A.err = reinterpret_cast<unsigned long long *>(err);
+  switch (mesh->dim * 100 + fe_order * 10 + defo->order) {
+    case 211: return launch_elvec_def<2, 1, 1>(A, dd->sm_count, nlist, st);
+    case 212: return launch_elvec_def<2, 1, 2>(A, dd->sm_count, nlist, st);
+    case 221: return launch_elvec_def<2, 2, 1>(A, dd->sm_count, nlist, st);
+    case 222: return launch_elvec_def<2, 2, 2>(A, dd->sm_count, nlist, st);
+    case 311: return launch_elvec_def<3, 1, 1>(A, dd->sm_count, nlist, st);
+    case 312: return launch_elvec_def<3, 1, 2>(A, dd->sm_count, nlist, st);
+    case 321: return launch_elvec_def<3, 2, 1>(A, dd->sm_count, nlist, st);
+    case 322: return launch_elvec_def<3, 2, 2>(A, dd->sm_count, nlist, st);
   }
   set_error("unsupported (dim, order, deformation order)");
   return NGSX_ERR_UNSUPPORTED;

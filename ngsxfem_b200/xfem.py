@@ -365,9 +365,10 @@ class SymbolicCutLFI:
     def __init__(self, lset, domain_type=NEG, force_intorder: int = -1, time_order: int = -1, subdivlvl: int = 0,
                  quad_dir_policy=OPTIMAL, form=None, VOL_or_BND=VOL, element_boundary: bool = False, skeleton: bool = False,
                  definedon=None, definedonelements: Optional[BitArray] = None, deformation=None):
-        if VOL_or_BND != VOL or element_boundary or skeleton or time_order >= 0 or subdivlvl != 0 or deformation is not None:
+        if VOL_or_BND != VOL or element_boundary or skeleton or time_order >= 0 or subdivlvl != 0:
             raise NgsxError(-2, "this SymbolicCutLFI variant is outside the CUDA path")
         self.lset, self.dt, self.force_intorder, self.definedonelements = lset, int(domain_type), force_intorder, definedonelements
+        self.deformation = deformation                     # lfi->SetDeformation (xfem/python_xfem.cpp:650-651); None: the mesh's
         # form = f * v with f a polynomial CoefficientFunction (py_tutorials/fictdom_ghostpen.py:98: coeff_f*v); on [Vh, Vhx]
         # f * (v_std + neg(v_x)) etc. (py_tutorials/nxfem.py:109-110): one scalar per test block {std, x NEG-masked, x POS-masked}
         names = {("v",): 0, ("xvn",): 1, ("xvp",): 2}
@@ -857,8 +858,6 @@ class LinearForm:
 
     def Assemble(self):
         """NGS/comp/linearform.cpp:209-243"""
-        if self.space.mesh.deformation is not None:
-            raise NgsxError(-2, "linear forms on a deformed mesh are outside the CUDA path (row f-4 covers BilinearForm + Integrate); no CPU fallback")
         L = _lib_()
         fes = self._h1
         if self.vec.numel() != self.space.ndof:                            # XFESpace.Update changed the number of x-dofs
@@ -866,6 +865,12 @@ class LinearForm:
             self._xplans.clear()
         self.vec.zero_()
         for k, integ in enumerate(self.integrators):
+            gfd = integ.deformation if getattr(integ, "deformation", None) is not None else fes.mesh.deformation
+            if gfd is not None:
+                if integ.has_x:
+                    raise NgsxError(-2, "neg / pos test functions on a deformed mesh are outside the CUDA path; no CPU fallback")
+                self._assemble_deformed(integ, k, gfd)
+                continue
             if integ.blocks[0] != 0.0:
                 if k not in self._plans:
                     ci = CutInfo(fes.mesh, integ.lset)
@@ -884,6 +889,36 @@ class LinearForm:
             if integ.has_x:
                 self._assemble_x(integ, k)
         return self
+
+    def _assemble_deformed(self, integ, k, gfd):
+        """deformed mesh (row f-4): dense element vectors with per-point geometry (ngsx_elvec_h1_deformed), then the per-dof gather
+        of AddElementVector (ngsx_gather_vec: entries of a dof in (element, local dof) order, no atomics)"""
+        L = _lib_()
+        fes = self._h1
+        if integ.blocks[0] == 0.0:
+            return
+        key = ("def", k)
+        if key not in self._xplans:
+            ci = CutInfo(fes.mesh, integ.lset)
+            ba = ci.GetElementsOfType({NEG: HASNEG, POS: HASPOS, IF: CDOM_IF}[integ.dt])
+            if integ.definedonelements is not None:
+                ba = ba & integ.definedonelements
+            els = ba.nonzero().to(torch.int32).contiguous()
+            n, nd = els.numel(), fes.nd
+            dof = fes.el2dof[els.long()].reshape(-1).long()
+            src = torch.arange(n * nd, device=dof.device)
+            order = torch.argsort(dof * max(n * nd, 1) + src)
+            dofptr = torch.zeros(fes.ndof + 1, dtype=torch.int64, device=dof.device)
+            dofptr[1:] = torch.cumsum(torch.bincount(dof, minlength=fes.ndof), 0)
+            self._xplans[key] = (els, dofptr, src[order].contiguous(), torch.empty((n, nd), dtype=torch.float64, device=dof.device))
+        els, dofptr, pairs, elvecs = self._xplans[key]
+        if els.numel() == 0:
+            return
+        poly = _poly_of(integ.coef)
+        defo = fes.mesh.c_deformation(gfd)
+        check(L.ngsx_elvec_h1_deformed(ctypes.byref(fes.mesh.c_struct()), ctypes.byref(defo), _ptr(_lset_vec(integ.lset)), fes.order, integ.dt,
+                                       integ.intorder(fes.order), ctypes.byref(poly), els.numel(), _ptr(els), _ptr(elvecs), None, None, _stream()))
+        check(L.ngsx_gather_vec(fes.ndof, _ptr(dofptr), _ptr(pairs), _ptr(elvecs), 1.0, 1, _ptr(self.vec), _stream()))
 
     def _assemble_x(self, integ, k):
         """x-dof part (DiffOpX<RNEG/RPOS> as test operator, xfem/xfemdiffops.cpp:30-40): the element vectors of the IF elements

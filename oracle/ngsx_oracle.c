@@ -638,6 +638,24 @@ int orc_elmat_h1_iso(int dim, int fe_order, int dord, const double *gcoef, const
   return np;
 }
 
+/* xfem/symboliccutlfi.cpp:52-158 T_CalcElementVector on a deformed element, f = sum_m c_m x^a y^b z^c at the mapped point */
+int orc_elvec_h1_iso(int dim, int fe_order, int dord, const double *gcoef, const double *ls, int dt, int intorder,
+                     int nmono, const double *mono, double *elvec)
+{
+  static _Thread_local double pts[3*ORC_MAXPTS], w[ORC_MAXPTS], meas[ORC_MAXPTS], xp[3*ORC_MAXPTS];
+  int np = orc_cut_rule_iso(dim, dord, gcoef, ls, dt, intorder, pts, w, meas, xp, ORC_MAXPTS);
+  int nd = orc_h1_ndof(dim, fe_order);
+  if (np < 0) return np;
+  for (int i = 0; i < nd; i++) elvec[i] = 0;
+  double shape[ORC_MAXND], dref[ORC_MAXND*3];
+  for (int q = 0; q < np; q++) {
+    orc_h1_shape(dim, fe_order, 0, pts + 3*q, shape, dref);
+    double pv = meas[q] * w[q] * eval_mono(nmono, mono, xp + 3*q);
+    for (int i = 0; i < nd; i++) elvec[i] += pv * shape[i];
+  }
+  return np;
+}
+
 /* coefficients of x(xi) on element e: vertex coordinates + deformation on the vertex dofs, deformation on the others */
 static void gather_iso(int dim, const int32_t *el2v, const double *vert, const double *lset_v, int ndg, const int32_t *el2dof_def,
                        const double *defo, int64_t e, double *gcoef, double *ls)
@@ -676,6 +694,24 @@ double orc_integrate_mesh_iso(int dim, int64_t ne, const int32_t *el2v, const do
   }
   if (npts_total) *npts_total = nptot;
   return sum;
+}
+
+int64_t orc_elvec_mesh_iso(int dim, int64_t nel, const int64_t *els, const int32_t *el2v, const double *vert, const double *lset_v,
+                           int dord, const int32_t *el2dof_def, const double *defo, int fe_order, int dt, int intorder,
+                           int nmono, const double *mono, double *elvecs, int32_t *npts)
+{
+  int nd = orc_h1_ndof(dim, fe_order), ndg = orc_h1_ndof(dim, dord);
+  int64_t nn = 0;
+#pragma omp parallel for schedule(dynamic,256) reduction(+:nn)
+  for (int64_t k = 0; k < nel; k++) {
+    int64_t e = els ? els[k] : k;
+    double gcoef[ORC_MAXND*3], ls[4];
+    gather_iso(dim, el2v, vert, lset_v, ndg, el2dof_def, defo, e, gcoef, ls);
+    int r = orc_elvec_h1_iso(dim, fe_order, dord, gcoef, ls, dt, intorder, nmono, mono, elvecs + (size_t)k*nd);
+    if (npts) npts[k] = r;
+    if (r < 0) memset(elvecs + (size_t)k*nd, 0, sizeof(double)*nd); else nn++;
+  }
+  return nn;
 }
 
 int64_t orc_elmat_mesh_iso(int dim, int64_t nel, const int64_t *els, const int32_t *el2v, const double *vert, const double *lset_v,

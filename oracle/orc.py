@@ -67,6 +67,9 @@ def load():
     L.orc_facetpatch_elmat_h1.argtypes = [c_int, c_int, ip, dp, ip, dp, c_double, c_int, dp]
     L.orc_cut_rule_iso.argtypes = [c_int, c_int, dp, dp, c_int, c_int, dp, dp, dp, dp, c_int]
     L.orc_elmat_h1_iso.argtypes = [c_int, c_int, c_int, dp, dp, c_int, c_int, dp, dp]
+    L.orc_elvec_h1_iso.argtypes = [c_int, c_int, c_int, dp, dp, c_int, c_int, c_int, dp, dp]
+    L.orc_elvec_mesh_iso.argtypes = [c_int, c_i64, lp, ip, dp, dp, c_int, ip, dp, c_int, c_int, c_int, c_int, dp, dp, ip]
+    L.orc_elvec_mesh_iso.restype = c_i64
     L.orc_integrate_mesh_iso.argtypes = [c_int, c_i64, ip, dp, dp, c_int, ip, dp, c_int, c_int, c_int, dp, lp]
     L.orc_integrate_mesh_iso.restype = c_double
     L.orc_elmat_mesh_iso.argtypes = [c_int, c_i64, lp, ip, dp, dp, c_int, ip, dp, c_int, c_int, c_int, dp, dp, ip]
@@ -363,4 +366,29 @@ def elmat_mesh_iso(dim, el2v, vert, lset_v, dord, el2dof_def, defo, fe_order, dt
         ee = np.ascontiguousarray(els, dtype=np.int64); nel, ep = len(ee), P(ee, lp)
     out = np.zeros((nel, nd, nd)); npts = np.zeros(nel, dtype=np.int32)
     load().orc_elmat_mesh_iso(dim, nel, ep, P(ev, ip), P(vt), P(ls), dord, P(ed, ip), P(df), fe_order, dt, intorder, P(f), P(out), P(npts, ip))
+    return out, npts
+
+
+def elvec_h1_iso(dim, fe_order, dord, gcoef, lset, dt, intorder, mono, impl="oracle"):
+    nd = load().orc_h1_ndof(dim, fe_order)
+    evv = np.zeros(nd)
+    gc = _d(gcoef); ls = _d(lset); mo = mono_array(mono)
+    if impl == "oracle":
+        n = load().orc_elvec_h1_iso(dim, fe_order, dord, P(gc), P(ls), dt, intorder, len(mo), P(mo), P(evv))
+    else:
+        from . import refload
+        n = refload.load().ref_elvec_h1_iso(ET[dim], fe_order, dord, P(gc), P(ls), dt, intorder, len(mo), P(mo), P(evv))
+    return n, evv
+
+
+def elvec_mesh_iso(dim, el2v, vert, lset_v, dord, el2dof_def, defo, fe_order, dt, intorder, mono, els=None, nthreads=0):
+    ev = _i(el2v); vt = _d(vert); ls = _d(lset_v); ed = _i(el2dof_def); df = _d(defo); mo = mono_array(mono)
+    nd = load().orc_h1_ndof(dim, fe_order)
+    load().orc_set_threads(nthreads)
+    if els is None:
+        nel, ep = ev.shape[0], None
+    else:
+        ee = np.ascontiguousarray(els, dtype=np.int64); nel, ep = len(ee), P(ee, lp)
+    out = np.zeros((nel, nd)); npts = np.zeros(nel, dtype=np.int32)
+    load().orc_elvec_mesh_iso(dim, nel, ep, P(ev, ip), P(vt), P(ls), dord, P(ed, ip), P(df), fe_order, dt, intorder, len(mo), P(mo), P(out), P(npts, ip))
     return out, npts

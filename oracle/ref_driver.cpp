@@ -150,6 +150,38 @@ int ElmatIso(int fe_order, int dord, const double * gcoef, const double * lset, 
   return np;
 }
 
+// as ElmatWork::Elvec below, on the isoparametric transformation
+template <ELEMENT_TYPE ET>
+int ElvecIso(int fe_order, int dord, const double * gcoef, const double * lset, int dt, int intorder,
+             int nmono, const double * mono, double * elvec_out, LocalHeap & lh)
+{
+  constexpr int D = ET_trait<ET>::DIM;
+  H1HighOrderFE<ET> fel(fe_order);
+  int nd = fel.GetNDof();
+  auto trafo = IsoTrafo<ET>(dord, gcoef, lh);
+  Vector<> lv(D+1);
+  for (int i = 0; i < D+1; i++) lv(i) = lset[i];
+  const IntegrationRule * ir = StraightCutIntegrationRule(lv, *trafo, DOMAIN_TYPE(dt), intorder, FIND_OPTIMAL, lh);
+  if (!ir) return -1;
+  int np = ir->Size();
+  MappedIntegrationRule<D,D> mir(*ir, *trafo, lh);
+  FlatVector<> elvec(nd, lh); elvec = 0.0;
+  FlatVector<> shape(nd, lh);
+  for (int i = 0; i < np; i++)
+    {
+      double x[3] = {0,0,0};
+      for (int d = 0; d < D; d++) x[d] = mir[i].GetPoint()(d);
+      double f = 0;
+      for (int m = 0; m < nmono; m++)
+        f += mono[4*m] * pow(x[0], mono[4*m+1]) * pow(x[1], mono[4*m+2]) * pow(x[2], mono[4*m+3]);
+      double pv = mir[i].GetMeasure() * (*ir)[i].Weight() * f;
+      fel.CalcShape((*ir)[i], shape);
+      elvec += pv * shape;
+    }
+  for (int i = 0; i < nd; i++) elvec_out[i] = elvec(i);
+  return np;
+}
+
 template <ELEMENT_TYPE ET>
 struct ElmatWork
 {
@@ -294,6 +326,17 @@ int ref_elmat_h1_iso(int et, int fe_order, int dord, const double * gcoef, const
   try {
     if (et == ET_TRIG) return ElmatIso<ET_TRIG>(fe_order, dord, gcoef, lset, dt, intorder, c_mass, c_stiff, elmat, lh);
     if (et == ET_TET) return ElmatIso<ET_TET>(fe_order, dord, gcoef, lset, dt, intorder, c_mass, c_stiff, elmat, lh);
+    return -4;
+  } catch (...) { return -2; }
+}
+
+int ref_elvec_h1_iso(int et, int fe_order, int dord, const double * gcoef, const double * lset, int dt, int intorder,
+                     int nmono, const double * mono, double * elvec)
+{
+  LocalHeap & lh = GetLH(); HeapReset hr(lh);
+  try {
+    if (et == ET_TRIG) return ElvecIso<ET_TRIG>(fe_order, dord, gcoef, lset, dt, intorder, nmono, mono, elvec, lh);
+    if (et == ET_TET) return ElvecIso<ET_TET>(fe_order, dord, gcoef, lset, dt, intorder, nmono, mono, elvec, lh);
     return -4;
   } catch (...) { return -2; }
 }

@@ -48,6 +48,7 @@ def load():
     L.ref_elvec_h1.argtypes = [c_int, c_int, ip, dp, dp, c_int, c_int, c_int, dp, dp]
     L.ref_cut_rule_iso.argtypes = [c_int, c_int, dp, dp, c_int, c_int, dp, dp, dp, dp, c_int]
     L.ref_elmat_h1_iso.argtypes = [c_int, c_int, c_int, dp, dp, c_int, c_int, c_double, c_double, dp]
+    L.ref_elvec_h1_iso.argtypes = [c_int, c_int, c_int, dp, dp, c_int, c_int, c_int, dp, dp]
     L.ref_cutinfo_mesh.argtypes = [c_int, c_long, ip, dp, dp, cp, dp, c_int]
     L.ref_cutinfo_mesh.restype = c_long
     L.ref_integrate_mesh.argtypes = [c_int, c_long, ip, dp, dp, c_int, c_int, c_int, dp, c_int, lp]

@@ -1038,11 +1038,39 @@ def test_deformed_unsupported_paths_raise(X):
     a += X.xfem.SymbolicBFI(levelset_domain={"levelset": gf, "domain_type": NEG}, form=u * v)
     with pytest.raises(X.lib.NgsxError):                                          # the coloured scatter is undeformed only
         a.Assemble()
-    f = X.xfem.LinearForm(Vh)
-    f += X.xfem.SymbolicLFI(levelset_domain={"levelset": gf, "domain_type": NEG}, form=1.0 * v)
-    with pytest.raises(X.lib.NgsxError):
-        f.Assemble()
     mesh.UnsetDeformation()
+
+
+@pytest.mark.parametrize("dim", [2, 3])
+@pytest.mark.parametrize("fo,dord", [(1, 1), (2, 2), (2, 1)])
+def test_deformed_linear_form_against_oracle(X, dim, fo, dord):
+    from oracle import orc
+    mesh, gf, defo, Vd = _deformed_setup(X, dim, dord, seed=21)
+    Vh = X.ngs.H1(mesh, order=fo)
+    v = Vh.TestFunction()
+    x, y = X.ngs.x, X.ngs.y
+    cf, mono = 1.0 + 2.0 * x * y - 0.5 * y * y, [(1.0, 0, 0, 0), (2.0, 1, 1, 0), (-0.5, 0, 2, 0)]
+    el2v, vert, ls = mesh.el2v.cpu().numpy(), mesh.vert.cpu().numpy(), gf.vec.cpu().numpy()
+    e2d = Vh.el2dof.cpu().numpy()
+    mesh.SetDeformation(defo)
+    for dt in (NEG, POS, IF):
+        f = X.xfem.LinearForm(Vh)
+        f += X.xfem.SymbolicLFI(levelset_domain={"levelset": gf, "domain_type": dt}, form=cf * v)
+        f.Assemble()
+        first = f.vec.clone()
+        f.Assemble()
+        assert torch.equal(first, f.vec)                                          # bitwise reproducible
+        ev, npts = orc.elvec_mesh_iso(dim, el2v, vert, ls, dord, Vd.el2dof.cpu().numpy(), defo.vec.cpu().numpy(), fo, dt,
+                                      f.integrators[0].intorder(fo), mono)
+        want = np.zeros(Vh.ndof)
+        np.add.at(want, e2d.reshape(-1), np.where(npts[:, None] >= 0, ev, 0.0).reshape(-1))
+        assert np.abs(first.cpu().numpy() - want).max() <= RTOL * np.abs(want).max()
+    # integrator-level deformation on the undeformed mesh gives the same vector
+    mesh.UnsetDeformation()
+    g = X.xfem.LinearForm(Vh)
+    g += X.xfem.SymbolicLFI(levelset_domain={"levelset": gf, "domain_type": IF}, form=cf * v, deformation=defo)
+    g.Assemble()
+    assert torch.equal(g.vec, first)
 
 
 def test_gather_wait_event_orders_only(X):

@@ -88,6 +88,12 @@ def test_deformed_rule_and_elmat_random(dim, dord):
                 assert a[0] == b[0]
                 if a[0] > 0:
                     assert np.abs(a[1] - b[1]).max() <= 1e-12 * np.abs(b[1]).max()
+                mono = [(1.0, 0, 0, 0), (2.0, 1, 1, 0), (-0.5, 0, 2, 0)]
+                a = orc.elvec_h1_iso(dim, fo, dord, gc, ls, dt, fo + 2, mono)
+                b = orc.elvec_h1_iso(dim, fo, dord, gc, ls, dt, fo + 2, mono, impl="ref")
+                assert a[0] == b[0]
+                if a[0] > 0:
+                    assert np.abs(a[1] - b[1]).max() <= 1e-12 * np.abs(b[1]).max()
 
 
 @pytest.mark.parametrize("dim", [2, 3])
