@@ -42,7 +42,7 @@ struct DefArgs {
   PolyDevD f;
   const int32_t *els;
   double *elmats; int32_t *npts;       // element matrices
-  double *partial;                     // Integrate: one partial per element (warp kernel) / per warp (thread kernel)
+  double *partial;                     // Integrate: one value per element
   unsigned long long *err;
   int32_t *worklist; int32_t *wcount;  // thread-per-element passes: list positions of the cut elements, their number
 };
@@ -616,9 +616,12 @@ __global__ void __launch_bounds__(TT) k_elvec_def_t(DefArgs A, int64_t count) {
   }
 }
 
-// Integrate, thread per element: uncut elements of the domain and cut elements inline (1.5 % of a mesh), warp butterfly ->
-// partial[warp]; the shape of every partial sum depends on ne only
-template <int DIM, int DORD>
+// Integrate, thread per element, two passes like the element matrices: pass 1 integrates the uncut elements of the domain into
+// val[e] and records the cut ones; pass 2 walks the recorded list and writes val[e] of the cut elements.  (Inline, a cut element --
+// 14..42 points -- held up its whole warp: 149 K cut elements touch more warps than the 59 K that carry NEG elements; measured
+// 1.28 ms inline.)  The values sit at their element's position, so the order of the work list never reaches the sum: the
+// fixed-shape tree over val[0..ne) is bitwise reproducible.
+template <int DIM, int DORD, bool CUTPASS>
 __global__ void __launch_bounds__(TT) k_int_def_t(DefArgs A, int64_t ne) {
   constexpr int NDG = H1<DIM, DORD>::ND;
   extern __shared__ __align__(16) unsigned char smem_raw[];
@@ -628,70 +631,68 @@ __global__ void __launch_bounds__(TT) k_int_def_t(DefArgs A, int64_t ne) {
   for (int i = threadIdx.x; i < A.nr_vol; i += TT) srule_vol[i] = A.rule_vol[i];
   for (int i = threadIdx.x; i < A.nr_if; i += TT) srule_if[i] = A.rule_if[i];
   __syncthreads();
-  const int64_t nround = (ne + TT - 1) / TT;
-  for (int64_t b = blockIdx.x; b < nround; b += gridDim.x) {
-    const int64_t e = b * TT + threadIdx.x;
+  const int64_t n = CUTPASS ? (int64_t)*A.wcount : ne;
+  for (int64_t w = (int64_t)blockIdx.x * TT + threadIdx.x; w < n; w += (int64_t)gridDim.x * TT) {
+    const int64_t e = CUTPASS ? (int64_t)A.worklist[w] : w;
+    int v[4];
+    load_vertices<DIM>(A.M, e, v);
+    double ls[4];
+#pragma unroll
+    for (int a = 0; a <= DIM; a++) ls[a] = __ldg(A.lset + v[a]);
+    int mask;
+    const int dom = sign_test<DIM>(ls, mask);
+    const bool cut = dom == IF;
+    if constexpr (!CUTPASS) {
+      if (cut) A.worklist[atomicAdd(A.wcount, 1)] = (int32_t)e;
+      if (cut || dom != A.dt) { A.partial[e] = 0.0; continue; }
+    }
     double sum = 0.0;
-    if (e < ne) {
-      int v[4];
-      load_vertices<DIM>(A.M, e, v);
-      double ls[4];
+    load_gc_thread<DIM, DORD>(A, e, v, gcs);
+    double r2 = 0.0;
 #pragma unroll
-      for (int a = 0; a <= DIM; a++) ls[a] = __ldg(A.lset + v[a]);
-      int mask;
-      const int dom = sign_test<DIM>(ls, mask);
-      const bool cut = dom == IF;
-      if (cut || dom == A.dt) {
-        load_gc_thread<DIM, DORD>(A, e, v, gcs);
-        double r2 = 0.0;
+    for (int a = 0; a < DIM; a++) { double d = ls[a] - ls[DIM]; r2 += d * d; }
+    const bool iface = CUTPASS && A.dt == IF;
+    CutEntry E;
+    if (CUTPASS) E = A.tab->e[DIM - 2][A.dt][mask]; else { E.ns = 1; E.npt = 0; }
+    const double4 *rule = iface ? srule_if : srule_vol;
+    const int nr = iface ? A.nr_if : A.nr_vol;
+    for (int s = 0; s < E.ns; s++) {
+      double P[4][3];
+      double sfac = 1.0;
+      if (CUTPASS) {
+        for (int a = 0; a < E.npt; a++) coded_point<DIM>(E.v[s][a], ls, P[a]);
+        sfac = simplex_factor(E.npt, P);
+      }
+      for (int q = 0; q < nr; q++) {
+        const double4 r = rule[q];
+        double xi[3] = {r.x, r.y, r.z};
+        if (CUTPASS) simplex_point(E.npt, P, r, xi);
+        double lam[4] = {xi[0], xi[1], xi[2], 0.0};
+        double last = 1.0;
 #pragma unroll
-        for (int a = 0; a < DIM; a++) { double d = ls[a] - ls[DIM]; r2 += d * d; }
-        const bool iface = cut && A.dt == IF;
-        CutEntry E;
-        if (cut) E = A.tab->e[DIM - 2][A.dt][mask]; else { E.ns = 1; E.npt = 0; }
-        const double4 *rule = iface ? srule_if : srule_vol;
-        const int nr = iface ? A.nr_if : A.nr_vol;
-        for (int s = 0; s < E.ns; s++) {
-          double P[4][3];
-          double sfac = 1.0;
-          if (cut) {
-            for (int a = 0; a < E.npt; a++) coded_point<DIM>(E.v[s][a], ls, P[a]);
-            sfac = simplex_factor(E.npt, P);
+        for (int a = 0; a < DIM; a++) last -= lam[a];
+        lam[DIM] = last;
+        double x[3] = {0.0, 0.0, 0.0}, gl[DIM + 1][DIM], det;
+        iso_point<DIM, DORD>(GcThread<TT>{gcs}, lam, x, gl, det);
+        double scale = 1.0;
+        if (iface) {
+          double g2 = 0.0;
+#pragma unroll
+          for (int d = 0; d < DIM; d++) {
+            double t = 0.0;
+#pragma unroll
+            for (int a = 0; a <= DIM; a++) t += ls[a] * gl[a][d];
+            g2 += t * t;
           }
-          for (int q = 0; q < nr; q++) {
-            const double4 r = rule[q];
-            double xi[3] = {r.x, r.y, r.z};
-            if (cut) simplex_point(E.npt, P, r, xi);
-            double lam[4] = {xi[0], xi[1], xi[2], 0.0};
-            double last = 1.0;
-#pragma unroll
-            for (int a = 0; a < DIM; a++) last -= lam[a];
-            lam[DIM] = last;
-            double x[3] = {0.0, 0.0, 0.0}, gl[DIM + 1][DIM], det;
-            iso_point<DIM, DORD>(GcThread<TT>{gcs}, lam, x, gl, det);
-            double scale = 1.0;
-            if (iface) {
-              double g2 = 0.0;
-#pragma unroll
-              for (int d = 0; d < DIM; d++) {
-                double t = 0.0;
-#pragma unroll
-                for (int a = 0; a <= DIM; a++) t += ls[a] * gl[a][d];
-                g2 += t * t;
-              }
-              scale = sqrt(g2) / sqrt(r2);
-            }
-            double fv = 0.0;
-            for (int m = 0; m < A.f.n; m++)
-              fv += A.f.c[m] * ipow(x[0], A.f.ex[m][0]) * ipow(x[1], A.f.ex[m][1]) * ipow(x[2], A.f.ex[m][2]);
-            sum += fabs(det) * (r.w * sfac * scale) * fv;
-          }
+          scale = sqrt(g2) / sqrt(r2);
         }
+        double fv = 0.0;
+        for (int m = 0; m < A.f.n; m++)
+          fv += A.f.c[m] * ipow(x[0], A.f.ex[m][0]) * ipow(x[1], A.f.ex[m][1]) * ipow(x[2], A.f.ex[m][2]);
+        sum += fabs(det) * (r.w * sfac * scale) * fv;
       }
     }
-#pragma unroll
-    for (int o = 16; o > 0; o >>= 1) sum += __shfl_xor_sync(0xffffffffu, sum, o);
-    if ((threadIdx.x & 31) == 0) A.partial[b * (TT / 32) + (threadIdx.x >> 5)] = sum;
+    A.partial[e] = sum;
   }
 }
 
@@ -794,9 +795,8 @@ static int launch_elvec_def(const DefArgs &A, int sm_count, int64_t nlist, cudaS
   return NGSX_OK;
 }
 
-// returns the number of partials through *npart
 template <int DIM, int DORD>
-static int launch_int_def(const DefArgs &A, int sm_count, int64_t ne, cudaStream_t st) {
+static int launch_int_def(DefArgs &A, int sm_count, int64_t ne, cudaStream_t st) {
   constexpr int NDG = H1<DIM, DORD>::ND;
   if (g_def_warp) {
     const size_t smem = DW * (size_t)NDG * DIM * 8;
@@ -807,12 +807,26 @@ static int launch_int_def(const DefArgs &A, int sm_count, int64_t ne, cudaStream
     NGSX_LAUNCH_CHECK();
     return NGSX_OK;
   }
+  int32_t *work = nullptr;
+  NGSX_CUDA(cudaMallocAsync(&work, (ne + 1) * sizeof(int32_t), st));
+  A.worklist = work + 1; A.wcount = work;
+  cudaError_t e0 = cudaMemsetAsync(work, 0, sizeof(int32_t), st);
   const size_t smem = (size_t)NDG * DIM * TT * 8 + (size_t)(A.nr_vol + A.nr_if) * 32;
-  auto kern = k_int_def_t<DIM, DORD>;
-  unsigned grid;
-  if (int rc = grid_threads(kern, smem, sm_count, ne, &grid)) return rc;
-  kern<<<grid, TT, smem, st>>>(A, ne);
-  NGSX_LAUNCH_CHECK();
+  auto k1 = k_int_def_t<DIM, DORD, false>;
+  auto k2 = k_int_def_t<DIM, DORD, true>;
+  unsigned g1 = 1, g2 = 1;
+  int rc = grid_threads(k1, smem, sm_count, ne, &g1);
+  if (!rc) rc = grid_threads(k2, smem, sm_count, ne, &g2);
+  if (!rc) {
+    k1<<<g1, TT, smem, st>>>(A, ne);
+    k2<<<g2, TT, smem, st>>>(A, ne);
+    g_launches.fetch_add(2);
+  }
+  cudaError_t e1 = cudaGetLastError();
+  cudaFreeAsync(work, st);
+  if (rc) return rc;
+  NGSX_CUDA(e0);
+  NGSX_CUDA(e1);
   return NGSX_OK;
 }
 
@@ -919,7 +933,7 @@ extern "C" int ngsx_integrate_deformed(const ngsx_mesh *mesh, const ngsx_deforma
   if (ne == 0) { NGSX_CUDA(cudaMemsetAsync(out, 0, sizeof(double), st)); return NGSX_OK; }
   A.f.n = h_f->nterms;
   for (int m = 0; m < A.f.n; m++) { A.f.c[m] = h_f->coef[m]; for (int d = 0; d < 3; d++) A.f.ex[m][d] = h_f->ex[m][d]; }
-  const int64_t npart = g_def_warp ? ne : ((ne + TT - 1) / TT) * (TT / 32);      // one partial per element / per warp of 32 elements
+  const int64_t npart = ne;                                                      // one value per element, at the element's position
   const unsigned nmid = (unsigned)std::min<int64_t>((npart + 255) / 256, 296);   // fixed upper bound: device-independent shape
   double *partial = nullptr;
   NGSX_CUDA(cudaMallocAsync(&partial, (npart + nmid) * sizeof(double), st));
