@@ -208,7 +208,13 @@ def Integrate(levelset_domain=None, cf=None, mesh=None, order=5, time_order=-1, 
         total = 0.0
         for f, sym in levelset_domain.parts:
             ld = sym.levelset_domain
-            total += Integrate(levelset_domain=ld, cf=f, mesh=mesh, order=ld.get("force_intorder", order), time_order=time_order)
+            saved = mesh.deformation
+            if sym.deformation is not None:                          # cf * dCut(..., deformation = gf): the symbol's deformation for this part
+                mesh.SetDeformation(sym.deformation)
+            try:
+                total += Integrate(levelset_domain=ld, cf=f, mesh=mesh, order=ld.get("force_intorder", order), time_order=time_order)
+            finally:
+                mesh.deformation = saved
         return total
     if levelset_domain is None or not isinstance(levelset_domain, dict):
         raise NgsxError(-2, "only Integrate(levelset_domain=...) is provided (plain NGSolve Integrate is not part of the path)")
@@ -238,14 +244,15 @@ class CutIntegrand:
 
 
 class CutDifferentialSymbol:
-    def __init__(self, levelset_domain, definedonelements=None):
-        self.levelset_domain, self.definedonelements = dict(levelset_domain), definedonelements
+    def __init__(self, levelset_domain, definedonelements=None, deformation=None):
+        self.levelset_domain, self.definedonelements, self.deformation = dict(levelset_domain), definedonelements, deformation
 
-    def __call__(self, definedonelements=None, levelset_domain=None, **kwargs):
+    def __call__(self, definedonelements=None, levelset_domain=None, deformation=None, **kwargs):
         ld = dict(self.levelset_domain if levelset_domain is None else levelset_domain)
         if "order" in kwargs and kwargs["order"] is not None:
             ld["force_intorder"] = int(kwargs["order"])
-        return CutDifferentialSymbol(ld, self.definedonelements if definedonelements is None else definedonelements)
+        return CutDifferentialSymbol(ld, self.definedonelements if definedonelements is None else definedonelements,
+                                     self.deformation if deformation is None else deformation)
 
     def __rmul__(self, form):
         return CutIntegrand([(form, self)])
@@ -253,22 +260,22 @@ class CutDifferentialSymbol:
 
 def dCut(levelset, domain_type, order=None, subdivlvl=None, time_order=-1, levelset_domain=None, definedonelements=None, **kwargs):
     """dCut(levelset, domain_type, order = None, ...): differential symbol of a cut integral (NEG / POS / IF part)"""
-    if time_order >= 0 or kwargs.get("deformation") is not None:
-        raise NgsxError(-2, "space-time / deformed dCut integrators are outside the CUDA path")
+    if time_order >= 0:
+        raise NgsxError(-2, "space-time dCut integrators are outside the CUDA path")
     ld = dict(levelset_domain) if levelset_domain is not None else {}
     ld.update({"levelset": levelset, "domain_type": domain_type})
     if order is not None:
         ld["force_intorder"] = int(order)
     if subdivlvl:
         ld["subdivlvl"] = subdivlvl
-    return CutDifferentialSymbol(ld, definedonelements)
+    return CutDifferentialSymbol(ld, definedonelements, kwargs.get("deformation"))
 
 
 def dx(levelset_domain=None, definedonelements=None, **kwargs):
     """dx(levelset_domain = {...}): the volume symbol restricted to a level-set domain (plain dx is NGSolve's, not part of the path)"""
     if levelset_domain is None:
         raise NgsxError(-2, "only dx(levelset_domain=...) is provided (uncut NGSolve integrators are not part of the path)")
-    return CutDifferentialSymbol(levelset_domain, definedonelements)
+    return CutDifferentialSymbol(levelset_domain, definedonelements, kwargs.get("deformation"))
 
 
 # ------------------------------------------------------------------------------------------------------------------
@@ -500,7 +507,8 @@ class BilinearForm:
     def __iadd__(self, integ):
         if isinstance(integ, CutIntegrand):                            # a += form * dCut(...) [+ form2 * dCut(...)]
             for form, sym in integ.parts:
-                self += SymbolicBFI(levelset_domain=sym.levelset_domain, form=form, definedonelements=sym.definedonelements)
+                self += SymbolicBFI(levelset_domain=sym.levelset_domain, form=form, definedonelements=sym.definedonelements,
+                                    deformation=sym.deformation)
             return self
         if not isinstance(integ, (SymbolicCutBFI, SymbolicFacetPatchBFI)):
             raise NgsxError(-2, "only SymbolicCutBFI / SymbolicFacetPatchBFI integrators are on the CUDA path")
@@ -847,7 +855,8 @@ class LinearForm:
     def __iadd__(self, integ):
         if isinstance(integ, CutIntegrand):                            # f += form * dCut(...)
             for form, sym in integ.parts:
-                self += SymbolicLFI(levelset_domain=sym.levelset_domain, form=form, definedonelements=sym.definedonelements)
+                self += SymbolicLFI(levelset_domain=sym.levelset_domain, form=form, definedonelements=sym.definedonelements,
+                                    deformation=sym.deformation)
             return self
         if not isinstance(integ, SymbolicCutLFI):
             raise NgsxError(-2, "only SymbolicCutLFI integrators are on the CUDA path")

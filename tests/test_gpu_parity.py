@@ -1101,3 +1101,49 @@ def test_gather_wait_event_orders_only(X):
         a.Assemble()                                                              # one-shot: no stale event on the next call
         assert torch.equal(a.mat.vals, ref)
     assert abs(float(s.item()) - 4 * np.pi * 0.35 ** 2) < 0.1
+
+
+def test_deformed_dcut_spelling_and_edge_cases(X):
+    """form * dCut(..., deformation = gf) == SymbolicBFI(..., deformation = gf); Integrate(cf * dCut(..., deformation = gf), mesh);
+    a level set the reference throws on is counted on the deformed path too; an empty element list is a no-op"""
+    mesh, gf, defo, Vd = _deformed_setup(X, 2, 2, seed=5)
+    Vh = X.ngs.H1(mesh, order=2)
+    u, v = Vh.TnT()
+    grad = X.ngs.grad
+    a = X.xfem.BilinearForm(Vh)
+    a += (grad(u) * grad(v) + u * v) * X.xfem.dCut(gf, NEG, deformation=defo)
+    a.Assemble()
+    b = X.xfem.BilinearForm(Vh)
+    b += X.xfem.SymbolicBFI(levelset_domain={"levelset": gf, "domain_type": NEG}, form=grad(u) * grad(v) + u * v, deformation=defo)
+    b.Assemble()
+    assert torch.equal(a.mat.vals, b.mat.vals)
+    c = X.xfem.BilinearForm(Vh)
+    c += X.xfem.SymbolicBFI(levelset_domain={"levelset": gf, "domain_type": NEG}, form=grad(u) * grad(v) + u * v)
+    c.Assemble()
+    assert not torch.equal(a.mat.vals, c.mat.vals)
+    i1 = X.xfem.Integrate(1.0 * X.xfem.dCut(gf, IF, order=2, deformation=defo), mesh)
+    assert mesh.deformation is None
+    mesh.SetDeformation(defo)
+    i2 = X.xfem.Integrate(levelset_domain={"levelset": gf, "domain_type": IF}, cf=1.0, mesh=mesh, order=2)
+    assert i1 == i2
+    # degenerate level set: exact zero on a cut element -> counted, raised by check_degenerate like on the affine path
+    bad = X.ngs.GridFunction(X.ngs.H1(mesh, order=1))
+    bad.vec.copy_(gf.vec)
+    ci = X.xfem.CutInfo(mesh, gf)
+    e = int(ci.GetElementsOfType(X.xfem.IF).nonzero()[0].item())
+    bad.vec[mesh.el2v[e, 0].long()] = 0.0
+    d = X.xfem.BilinearForm(Vh)
+    d += X.xfem.SymbolicBFI(levelset_domain={"levelset": bad, "domain_type": NEG}, form=u * v)
+    d.Assemble()
+    with pytest.raises(X.lib.NgsxError):
+        d.check_degenerate()
+    # empty list through the C ABI
+    L = X.lib.load()
+    dd = mesh.c_deformation()
+    f = X.lib.FormH1(); f.c_mass = 1.0
+    assert L.ngsx_elmat_h1_deformed(ctypes.byref(mesh.c_struct()), ctypes.byref(dd), gf.vec.data_ptr(), 2, NEG, 4, ctypes.byref(f), 0, None, None,
+                                    None, None, None) == 0
+    dd.order = 3
+    assert L.ngsx_elmat_h1_deformed(ctypes.byref(mesh.c_struct()), ctypes.byref(dd), gf.vec.data_ptr(), 2, NEG, 4, ctypes.byref(f), 0, None, None,
+                                    None, None, None) == -2
+    mesh.UnsetDeformation()
