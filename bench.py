@@ -147,7 +147,6 @@ def run_b200(args):
     torch.cuda.set_device(lrank)
     dev = f"cuda:{lrank}"
     if world > 1:
-        os.environ.setdefault("NCCL_DEBUG_FILE", "/dev/stderr")        # NCCL's version / debug lines must not land beside the JSON line on stdout
         dist.init_process_group("nccl", device_id=torch.device(dev))
     import __graft_entry__ as ge
     if rank == 0:
@@ -552,6 +551,16 @@ def run_reference(args):
 
 if __name__ == "__main__":
     args = parse()
+    # the contract is ONE JSON line on stdout: everything else that writes to file descriptor 1 (NCCL's version line, library
+    # chatter) goes to stderr; the JSON line is written to the saved descriptor
+    sys.stdout.flush()
+    _real_stdout = os.fdopen(os.dup(1), "w")
+    os.dup2(2, 1)
+    _print = print
+
+    def print(*a, **k):                                   # noqa: A001  (module-level: run_b200 / run_reference pick it up)
+        k.setdefault("file", _real_stdout)
+        _print(*a, **k)
     if args.impl == "reference":
         run_reference(args)
     else:
