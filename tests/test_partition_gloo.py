@@ -40,6 +40,18 @@ def _worker(rank, world, port, out):
     part, _ = orc.integrate_mesh(3, m.el2v[elo:ehi].numpy(), m.vert.numpy(), ls.numpy(), 0, 4)
     s = torch.tensor([part], dtype=torch.float64)
     dist.all_reduce(s)
+    # cost-weighted element blocks of the sweeps (a cut element = 40 sign tests): they tile [0, ne), every rank derives the same
+    # boundaries, the weights balance, and the all-reduced interface integral over them is the single-rank one
+    wts = 1.0 + 40.0 * (haspos & hasneg).to(torch.float64)
+    wb = partition.element_blocks_weighted(wts, world)
+    assert wb[0][0] == 0 and wb[-1][1] == m.ne and all(wb[r][1] == wb[r + 1][0] for r in range(world - 1))
+    share = float(wts[wb[rank][0]:wb[rank][1]].sum() / wts.sum())
+    assert abs(share - 1.0 / world) < 0.05
+    wpart, _ = orc.integrate_mesh(3, m.el2v[wb[rank][0]:wb[rank][1]].numpy(), m.vert.numpy(), ls.numpy(), 2, 4)
+    ws = torch.tensor([wpart], dtype=torch.float64)
+    dist.all_reduce(ws)
+    wfull, _ = orc.integrate_mesh(3, m.el2v.numpy(), m.vert.numpy(), ls.numpy(), 2, 4)
+    assert abs(float(ws) - wfull) <= 1e-13 * abs(wfull)
     if rank == 0:
         full, _ = orc.integrate_mesh(3, m.el2v.numpy(), m.vert.numpy(), ls.numpy(), 0, 4)
         out.put(dict(blocks=blocks, pairs=[int(x) for x in allp], total=int(d.numel()), sum=float(s), full=float(full), ndof=ndof))
