@@ -59,7 +59,7 @@ template <int DIM, int ORDER> struct Smem {
 };
 
 template <int DIM>
-__device__ __forceinline__ void load_el(const ngsx_mesh &M, const double *__restrict__ lset, int64_t e, double *ls, double (*p)[DIM]) {
+__device__ __forceinline__ void load_el(const ngsx_mesh &M, const double *__restrict__ lset, int64_t e, double *ls, double (*p)[DIM], int *v_out = nullptr) {
   int v[4];
   if constexpr (DIM == 3) {
     int4 q = __ldg(reinterpret_cast<const int4 *>(M.el2v) + e);
@@ -73,6 +73,7 @@ __device__ __forceinline__ void load_el(const ngsx_mesh &M, const double *__rest
     ls[k] = __ldg(lset + v[k]);
 #pragma unroll
     for (int d = 0; d < DIM; d++) p[k][d] = __ldg(M.vert + (int64_t)v[k] * DIM + d);
+    if (v_out) v_out[k] = v[k];
   }
 }
 
@@ -107,7 +108,7 @@ __global__ void __launch_bounds__(WARPS * 32) k_elmat(ElmatArgs A, int64_t first
   for (int i = threadIdx.x; i < A.nr_if; i += blockDim.x) srule_if[i] = A.rule_if[i];
   if (threadIdx.x < 16) lut[threadIdx.x] = A.tab->e[DIM - 2][A.dt][threadIdx.x];
   __syncthreads();
-  const bool fast = A.use_fast && A.dt != IF;
+  const bool fast = A.use_fast && A.dt != IF && ORDER < 3;      // order 3: the edge functions depend on the element's vertex numbers
   if (fast) {
     double glr[DIM + 1][DIM];                      // reference gradients of the barycentrics
 #pragma unroll
@@ -164,7 +165,9 @@ __global__ void __launch_bounds__(WARPS * 32) k_elmat(ElmatArgs A, int64_t first
       const int64_t kk = A.sublist ? A.sublist[k] : k;
       const int64_t e = A.els ? A.els[kk] : kk;
       double ls[4], p[DIM + 1][DIM];
-      load_el<DIM>(A.M, A.lset, e, ls, p);
+      int vn[4];
+      load_el<DIM>(A.M, A.lset, e, ls, p, vn);
+      const unsigned orient = ORDER == 3 ? edge_orientation<DIM>(vn) : 0u;
       int mask;
       const int dom = sign_test<DIM>(ls, mask);
       const bool cut = dom == IF;
@@ -254,7 +257,7 @@ __global__ void __launch_bounds__(WARPS * 32) k_elmat(ElmatArgs A, int64_t first
 #pragma unroll
                 for (int i = 0; i < ND; i++) {
                   double sv, gv[DIM];
-                  h1_shape_grad<DIM, ORDER>(i, lam, gl, sv, gv);
+                  h1_shape_grad<DIM, ORDER>(i, lam, gl, sv, gv, orient);
                   stage[lane * ND + i] = make_double4(sv, gv[0], gv[1], DIM == 3 ? gv[DIM - 1] : 0.0);
                 }
                 facq[lane] = meas * (r.w * sfac * scale);
@@ -460,12 +463,13 @@ static int configure(K kernel, size_t smem, int sm_count, int64_t nwarp_items, u
 }
 
 static int fill_common(const ngsx_mesh *mesh, const double *lset_v, int fe_order, int dt, int intorder, const DeviceData **dd,
-                       const double4 **rv, int *nv, const double4 **ri, int *ni) {
+                       const double4 **rv, int *nv, const double4 **ri, int *ni, int max_order = 2) {
   NGSX_REQUIRE(mesh && (mesh->dim == 2 || mesh->dim == 3), "mesh.dim must be 2 or 3");
   NGSX_REQUIRE(lset_v && mesh->vert && mesh->el2v, "mesh / level-set arrays are NULL");
   NGSX_REQUIRE(dt >= 0 && dt <= 2, "domain_type must be NEG, POS or IF");
-  if (fe_order < 1 || fe_order > 2) {
-    set_error("H1 order outside the CUDA path (supported: 1, 2); no CPU fallback");
+  if (fe_order < 1 || fe_order > max_order) {
+    set_error(max_order == 3 ? "H1 order outside the CUDA path (supported: 1, 2, 3); no CPU fallback"
+                             : "H1 order outside this entry point (supported: 1, 2; order 3: ngsx_elmat_h1 / ngsx_assemble_csr_h1); no CPU fallback");
     return NGSX_ERR_UNSUPPORTED;
   }
   *dd = device_data();
@@ -502,6 +506,8 @@ static int dispatch_elmat(const ElmatArgs &A, int fe_order, int sm_count, int nc
     case 22: return launch_elmat<2, 2, SINK>(A, sm_count, ncolors, h_color_ptr, nlist, st);
     case 31: return launch_elmat<3, 1, SINK>(A, sm_count, ncolors, h_color_ptr, nlist, st);
     case 32: return launch_elmat<3, 2, SINK>(A, sm_count, ncolors, h_color_ptr, nlist, st);
+    case 23: return launch_elmat<2, 3, SINK>(A, sm_count, ncolors, h_color_ptr, nlist, st);
+    case 33: return launch_elmat<3, 3, SINK>(A, sm_count, ncolors, h_color_ptr, nlist, st);
   }
   set_error("unsupported (dim, order)");
   return NGSX_ERR_UNSUPPORTED;
@@ -1078,7 +1084,7 @@ int ngsx_elmat_h1(const ngsx_mesh *mesh, const double *lset_v, int fe_order, int
                   int64_t nlist, const int32_t *els, double *elmats, int32_t *npts, void *stream) {
   const DeviceData *dd; const double4 *rv, *ri; int nv, ni;
   NGSX_REQUIRE(h_form && (nlist == 0 || elmats) && nlist >= 0, "elmat_h1: bad arguments");
-  if (int rc = fill_common(mesh, lset_v, fe_order, dt, intorder, &dd, &rv, &nv, &ri, &ni)) return rc;
+  if (int rc = fill_common(mesh, lset_v, fe_order, dt, intorder, &dd, &rv, &nv, &ri, &ni, 3)) return rc;
   if (nlist == 0) return NGSX_OK;
   ElmatArgs A{};
   A.M = *mesh; A.lset = lset_v; A.tab = dd->cut_table; A.dt = dt;
@@ -1095,7 +1101,7 @@ int ngsx_assemble_csr_h1(const ngsx_mesh *mesh, const double *lset_v, int fe_ord
   const DeviceData *dd; const double4 *rv, *ri; int nv, ni;
   NGSX_REQUIRE(h_form && nlist >= 0 && ncolors >= 0 && group >= 1 && h_color_ptr, "assemble_csr_h1: bad arguments");
   NGSX_REQUIRE(nlist == 0 || (slots && vals), "assemble_csr_h1: slots / vals are NULL");
-  if (int rc = fill_common(mesh, lset_v, fe_order, dt, intorder, &dd, &rv, &nv, &ri, &ni)) return rc;
+  if (int rc = fill_common(mesh, lset_v, fe_order, dt, intorder, &dd, &rv, &nv, &ri, &ni, 3)) return rc;
   if (nlist == 0) return NGSX_OK;
   ElmatArgs A{};
   A.M = *mesh; A.lset = lset_v; A.tab = dd->cut_table; A.dt = dt;

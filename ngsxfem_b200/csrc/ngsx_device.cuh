@@ -141,9 +141,16 @@ __device__ __forceinline__ void simplex_point(int n, const double (*P)[3], const
 // edge order (NGS/fem/elementtopology.cpp:143-146 trig {2,0},{1,2},{0,1}; :161-167 tet {3,0},{3,1},{3,2},{0,1},{0,2},{1,2}).
 // ---------------------------------------------------------------------------------------------------------------
 template <int DIM, int ORDER> struct H1 {
-  static constexpr int ND = (ORDER == 1) ? (DIM + 1) : (DIM == 2 ? 6 : 10);
   static constexpr int NEDGE = (DIM == 2) ? 3 : 6;
+  static constexpr int NFACE = (DIM == 2) ? 1 : 4;        // order 3: one face / cell function lam_a lam_b lam_c each
+  static constexpr int ND = (ORDER == 1) ? (DIM + 1) : (ORDER == 2 ? (DIM == 2 ? 6 : 10) : (DIM + 1 + 2 * NEDGE + NFACE));
 };
+
+// order 3 (element matrices only): per edge the pair {-1/2 lam_a lam_b, -1/2 x lam_a lam_b}, x = lam_e1 - lam_e0 with e0 the edge
+// vertex of the SMALLER global number (vertex-oriented edge, NGS/fem/h1hofe_impl.hpp:78-108, 250-312; IntLegNoBubble P0 = -1/2,
+// P1 = -x/2, NGS/fem/recursive_pol.hpp:1372-1374), then per face lam_a lam_b lam_c (DubinerBasis of order 0: orientation free;
+// tet faces NGS/fem/elementtopology.cpp {3,1,2},{3,2,0},{3,0,1},{0,2,1}).  orient: bit e set = edge e runs against its local order.
+
 
 template <int DIM> __device__ __forceinline__ void edge_vertices(int e, int &a, int &b) {
   if constexpr (DIM == 2) {
@@ -153,6 +160,20 @@ template <int DIM> __device__ __forceinline__ void edge_vertices(int e, int &a, 
     a = (e < 3) ? 3 : (e < 5 ? 0 : 1);
     b = (e < 3) ? e : (e == 3 ? 1 : 2);
   }
+}
+
+template <int DIM>
+__device__ __forceinline__ unsigned edge_orientation(const int *v) {
+  unsigned o = 0;
+#pragma unroll
+  for (int e = 0; e < H1<DIM, 3>::NEDGE; e++) {
+    int a, b;
+    edge_vertices<DIM>(e, a, b);
+    const int va = a == 0 ? v[0] : (a == 1 ? v[1] : (a == 2 ? v[2] : v[DIM]));
+    const int vb = b == 0 ? v[0] : (b == 1 ? v[1] : (b == 2 ? v[2] : v[DIM]));
+    o |= (va > vb) ? (1u << e) : 0u;
+  }
+  return o;
 }
 
 // shape value of dof i at barycentrics lam
@@ -166,22 +187,54 @@ __device__ __forceinline__ double h1_shape(int i, const double *lam) {
 
 // shape value + gradient w.r.t. the coordinates in which gl[k][:] (gradients of the barycentrics) are given
 template <int DIM, int ORDER>
-__device__ __forceinline__ void h1_shape_grad(int i, const double *lam, const double (*gl)[DIM], double &s, double *g) {
+__device__ __forceinline__ void h1_shape_grad(int i, const double *lam, const double (*gl)[DIM], double &s, double *g, unsigned orient = 0) {
   if (i <= DIM) {
     s = sel4(lam, i);
 #pragma unroll
     for (int d = 0; d < DIM; d++) g[d] = (i == 0 ? gl[0][d] : (i == 1 ? gl[1][d] : (i == 2 ? gl[2][d] : gl[DIM][d])));
     return;
   }
-  int a, b;
-  edge_vertices<DIM>(i - (DIM + 1), a, b);
-  double la = sel4(lam, a), lb = sel4(lam, b);
-  s = -0.5 * la * lb;
+  constexpr int NEDGE = H1<DIM, ORDER>::NEDGE;
+  constexpr int PER = ORDER == 3 ? 2 : 1;                 // functions per edge
+  const int r = i - (DIM + 1);
+  if (ORDER < 3 || r < PER * NEDGE) {
+    const int e = r / PER, k = r % PER;
+    int a, b;
+    edge_vertices<DIM>(e, a, b);
+    double la = sel4(lam, a), lb = sel4(lam, b);
+    if (ORDER == 3 && k == 1) {
+      const double sg = ((orient >> e) & 1u) ? -1.0 : 1.0;      // x = sg (lam_b - lam_a)
+      const double c = la * lb, x = sg * (lb - la);
+      s = -0.5 * x * c;
+#pragma unroll
+      for (int d = 0; d < DIM; d++) {
+        double ga = (a == 0 ? gl[0][d] : (a == 1 ? gl[1][d] : (a == 2 ? gl[2][d] : gl[DIM][d])));
+        double gb = (b == 0 ? gl[0][d] : (b == 1 ? gl[1][d] : (b == 2 ? gl[2][d] : gl[DIM][d])));
+        g[d] = -0.5 * (sg * (gb - ga) * c + x * (ga * lb + la * gb));
+      }
+      return;
+    }
+    s = -0.5 * la * lb;
+#pragma unroll
+    for (int d = 0; d < DIM; d++) {
+      double ga = (a == 0 ? gl[0][d] : (a == 1 ? gl[1][d] : (a == 2 ? gl[2][d] : gl[DIM][d])));
+      double gb = (b == 0 ? gl[0][d] : (b == 1 ? gl[1][d] : (b == 2 ? gl[2][d] : gl[DIM][d])));
+      g[d] = -0.5 * (ga * lb + la * gb);
+    }
+    return;
+  }
+  // order 3 face / cell function
+  const int f = r - PER * NEDGE;
+  int a = 0, b = 1, c = 2;
+  if (DIM == 3) { a = f == 3 ? 0 : 3; b = f == 0 ? 1 : (f == 1 ? 2 : (f == 2 ? 0 : 2)); c = f == 0 ? 2 : (f == 1 ? 0 : 1); }
+  const double la = sel4(lam, a), lb = sel4(lam, b), lc = sel4(lam, c);
+  s = la * lb * lc;
 #pragma unroll
   for (int d = 0; d < DIM; d++) {
     double ga = (a == 0 ? gl[0][d] : (a == 1 ? gl[1][d] : (a == 2 ? gl[2][d] : gl[DIM][d])));
     double gb = (b == 0 ? gl[0][d] : (b == 1 ? gl[1][d] : (b == 2 ? gl[2][d] : gl[DIM][d])));
-    g[d] = -0.5 * (ga * lb + la * gb);
+    double gc = (c == 0 ? gl[0][d] : (c == 1 ? gl[1][d] : (c == 2 ? gl[2][d] : gl[DIM][d])));
+    g[d] = ga * lb * lc + la * gb * lc + la * lb * gc;
   }
 }
 

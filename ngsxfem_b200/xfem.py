@@ -716,17 +716,24 @@ class BilinearForm:
                 self._assemble_facetpatch(integ, plan)
             elif integ.xterms is not None:
                 x_blocks += self._assemble_x(integ, plan, k, x_blocks)
-            elif isinstance(plan, _RowPlan) and self._deformation_of(integ) is not None:
-                # deformed elements (row f-4): per-point geometry -> dense blocks of the listed elements, then the
-                # owner-computes gather (each CSR value written once, plan order, no atomics)
+            elif isinstance(plan, _RowPlan) and (self._deformation_of(integ) is not None or fes.order >= 3):
+                # deformed elements (row f-4: per-point geometry) and H1 order 3 (orientation-dependent edge functions: no shared
+                # constant-rule table): dense blocks of the listed elements, then the owner-computes gather (each CSR value
+                # written once, plan order, no atomics)
                 lv = _lset_vec(integ.lset)
-                defo = fes.mesh.c_deformation(self._deformation_of(integ))
                 n = plan.els.numel()
                 if getattr(plan, "mats", None) is None:
                     plan.mats = torch.empty((n, fes.nd * fes.nd), dtype=torch.float64, device=fes.mesh.device)
-                check(L.ngsx_elmat_h1_deformed(mesh_c, ctypes.byref(defo), _ptr(lv), fes.order, integ.dt, integ.intorder(fes.order),
-                                               ctypes.byref(integ.form), n, _ptr(plan.els), _ptr(plan.mats), None, _ptr(self._err[k]), _stream()))
-                self._err_armed = True
+                if self._deformation_of(integ) is not None:
+                    if fes.order >= 3:
+                        raise NgsxError(-2, "H1 order 3 on a deformed mesh is outside the CUDA path; no CPU fallback")
+                    defo = fes.mesh.c_deformation(self._deformation_of(integ))
+                    check(L.ngsx_elmat_h1_deformed(mesh_c, ctypes.byref(defo), _ptr(lv), fes.order, integ.dt, integ.intorder(fes.order),
+                                                   ctypes.byref(integ.form), n, _ptr(plan.els), _ptr(plan.mats), None, _ptr(self._err[k]), _stream()))
+                    self._err_armed = True
+                else:
+                    check(L.ngsx_elmat_h1(mesh_c, _ptr(lv), fes.order, integ.dt, integ.intorder(fes.order), ctypes.byref(integ.form), n,
+                                          _ptr(plan.els), _ptr(plan.mats), None, _stream()))
                 check(L.ngsx_assemble_csr_rows_mats(plan.handle, _ptr(plan.mats), 0 if overwrite else 1, _ptr(self.mat.vals), _stream()))
             elif isinstance(plan, _RowPlan):
                 lv = _lset_vec(integ.lset)

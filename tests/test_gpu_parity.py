@@ -1147,3 +1147,54 @@ def test_deformed_dcut_spelling_and_edge_cases(X):
     assert L.ngsx_elmat_h1_deformed(ctypes.byref(mesh.c_struct()), ctypes.byref(dd), gf.vec.data_ptr(), 2, NEG, 4, ctypes.byref(f), 0, None, None,
                                     None, None, None) == -2
     mesh.UnsetDeformation()
+
+
+# ------------------------------------------------------------------------------------------------------------------
+# H1 order 3 (orientation-dependent edge functions + face / cell functions): element matrices and assembly
+# ------------------------------------------------------------------------------------------------------------------
+@pytest.mark.parametrize("dim,nx", [(2, 16), (3, 6)])
+def test_order3_elmats_and_assembly(X, dim, nx):
+    from oracle import orc
+    m = X.meshes.MakeStructured2DMesh(nx) if dim == 2 else X.meshes.MakeStructured3DMesh(nx)
+    mesh = X.ngs.Mesh(m)
+    gf = X.ngs.GridFunction(X.ngs.H1(mesh, order=1))
+    X.xfem.InterpolateToP1(X.ngs.SphereLevelset((0.5,) * dim, 0.35), gf)
+    rng = np.random.default_rng(33)
+    gf.vec += dev(1e-3 * rng.uniform(-1, 1, mesh.nv))
+    fo = 3
+    Vh = X.ngs.H1(mesh, order=fo)
+    assert Vh.nd == (10 if dim == 2 else 20)
+    u, v = Vh.TnT()
+    el2v, vert, ls = mesh.el2v.cpu().numpy(), mesh.vert.cpu().numpy(), gf.vec.cpu().numpy()
+    for dt in (NEG, POS, IF):
+        form = 0.7 * X.ngs.grad(u) * X.ngs.grad(v) + 1.3 * u * v
+        a = X.xfem.BilinearForm(Vh)
+        a += X.xfem.SymbolicBFI(levelset_domain={"levelset": gf, "domain_type": dt}, form=form)
+        io = a.integrators[0].intorder(fo)
+        assert io == 2 * fo
+        els, em, npts = a.elmats()
+        ref, rnp = orc.elmat_mesh(dim, el2v, vert, ls, fo, dt, io, 1.3, 0.7, els=els.cpu().numpy())
+        assert len(els) > 0 and np.array_equal(npts.cpu().numpy(), np.maximum(rnp, 0))
+        assert relerr_rows(em.cpu().numpy(), ref) <= RTOL
+        want = None
+        for mode in ("rows", "colored"):
+            b = X.xfem.BilinearForm(Vh)
+            b.assembly = mode
+            b += X.xfem.SymbolicBFI(levelset_domain={"levelset": gf, "domain_type": dt}, form=form)
+            b.Assemble()
+            assert b.assembly == mode
+            first = b.mat.vals.clone()
+            b.mat.vals.fill_(float("nan"))
+            b.Assemble()
+            assert torch.equal(first, b.mat.vals)
+            if want is None:
+                allels = np.arange(mesh.ne, dtype=np.int32)
+                want, _ = orc.assemble_csr(dim, el2v, vert, ls, fo, Vh.el2dof.cpu().numpy(), dt, io, 1.3, 0.7, np.array([0, mesh.ne]), allels,
+                                           b.mat.rowptr.cpu().numpy(), b.mat.colidx.cpu().numpy(), nthreads=1)
+            assert np.abs(first.cpu().numpy() - want).max() <= RTOL * np.abs(want).max()
+    # order 4 stays outside
+    with pytest.raises((X.lib.NgsxError, AssertionError)):
+        V4 = X.ngs.H1(mesh, order=4)
+        c = X.xfem.BilinearForm(V4)
+        c += X.xfem.SymbolicBFI(levelset_domain={"levelset": gf, "domain_type": NEG}, form=u * v)
+        c.Assemble()
