@@ -137,7 +137,8 @@ int ngsx_rule_fill(const ngsx_mesh *mesh, const double *lset_v, int dt, int orde
 /* els: [nlist] element numbers (NULL: 0..nlist-1).  elmats: [nlist][nd][nd] row-major (rows = test functions), zero where
  * the reference adds nothing; npts (may be NULL): rule size used per listed element.  fe_order 1..3, H1HighOrderFE basis (order 3:
  * vertex-oriented edge functions from the global vertex numbers in el2v + face / cell functions, NGS/fem/h1hofe_impl.hpp:78-108, 250-312;
- * ngsx_elmat_h1 and ngsx_assemble_csr_h1 only -- the row-gather entry point, element vectors and deformed meshes stay at 1..2).
+ * ngsx_elmat_h1, ngsx_assemble_csr_h1, ngsx_elvec_h1 and ngsx_assemble_vec_h1 -- the row-gather entry point, XFEM blocks, facet patches and
+ * deformed meshes stay at 1..2).
  * intorder < 0: the reference's default 2*fe_order - (difforders) is NOT guessed here -- the caller passes it. */
 int ngsx_elmat_h1(const ngsx_mesh *mesh, const double *lset_v, int fe_order, int dt, int intorder, const ngsx_form_h1 *h_form,
                   int64_t nlist, const int32_t *els, double *elmats, int32_t *npts, void *stream);

@@ -350,7 +350,9 @@ __global__ void __launch_bounds__(WARPS * 32) k_elvec(ElvecArgs A, int64_t first
     for (int64_t k = kb; k < ke; k++) {
       const int64_t e = A.els ? A.els[k] : k;
       double ls[4], p[DIM + 1][DIM];
-      load_el<DIM>(A.M, A.lset, e, ls, p);
+      int vn[4];
+      load_el<DIM>(A.M, A.lset, e, ls, p, vn);
+      const unsigned orient = ORDER == 3 ? edge_orientation<DIM>(vn) : 0u;
       int mask;
       const int dom = sign_test<DIM>(ls, mask);
       const bool cut = dom == IF;
@@ -412,7 +414,7 @@ __global__ void __launch_bounds__(WARPS * 32) k_elvec(ElvecArgs A, int64_t first
               for (int m = 0; m < A.f.n; m++)
                 fx += A.f.c[m] * ipow(x[0], A.f.ex[m][0]) * ipow(x[1], A.f.ex[m][1]) * ipow(x[2], A.f.ex[m][2]);
 #pragma unroll
-              for (int i = 0; i < ND; i++) stage[lane * ND + i] = h1_shape<DIM, ORDER>(i, lam);
+              for (int i = 0; i < ND; i++) stage[lane * ND + i] = h1_shape<DIM, ORDER>(i, lam, orient);
               facq[lane] = meas * (r.w * sfac * scale) * fx;
             }
             __syncwarp();
@@ -538,6 +540,8 @@ static int dispatch_elvec(const ElvecArgs &A, int fe_order, int sm_count, int nc
     case 22: return launch_elvec<2, 2, SINK>(A, sm_count, ncolors, h_color_ptr, nlist, st);
     case 31: return launch_elvec<3, 1, SINK>(A, sm_count, ncolors, h_color_ptr, nlist, st);
     case 32: return launch_elvec<3, 2, SINK>(A, sm_count, ncolors, h_color_ptr, nlist, st);
+    case 23: return launch_elvec<2, 3, SINK>(A, sm_count, ncolors, h_color_ptr, nlist, st);
+    case 33: return launch_elvec<3, 3, SINK>(A, sm_count, ncolors, h_color_ptr, nlist, st);
   }
   set_error("unsupported (dim, order)");
   return NGSX_ERR_UNSUPPORTED;
@@ -1178,7 +1182,7 @@ int ngsx_elvec_h1(const ngsx_mesh *mesh, const double *lset_v, int fe_order, int
                   int64_t nlist, const int32_t *els, double *elvecs, int32_t *npts, void *stream) {
   const DeviceData *dd; const double4 *rv, *ri; int nv, ni;
   NGSX_REQUIRE((nlist == 0 || elvecs) && nlist >= 0, "elvec_h1: bad arguments");
-  if (int rc = fill_common(mesh, lset_v, fe_order, dt, intorder, &dd, &rv, &nv, &ri, &ni)) return rc;
+  if (int rc = fill_common(mesh, lset_v, fe_order, dt, intorder, &dd, &rv, &nv, &ri, &ni, 3)) return rc;
   ElvecArgs A{};
   if (int rc = fill_poly(h_f, A.f)) return rc;
   if (nlist == 0) return NGSX_OK;
@@ -1194,7 +1198,7 @@ int ngsx_assemble_vec_h1(const ngsx_mesh *mesh, const double *lset_v, int fe_ord
   const DeviceData *dd; const double4 *rv, *ri; int nv, ni;
   NGSX_REQUIRE(nlist >= 0 && ncolors >= 0 && group >= 1 && h_color_ptr, "assemble_vec_h1: bad arguments");
   NGSX_REQUIRE(nlist == 0 || (el2dof_list && vec), "assemble_vec_h1: el2dof_list / vec are NULL");
-  if (int rc = fill_common(mesh, lset_v, fe_order, dt, intorder, &dd, &rv, &nv, &ri, &ni)) return rc;
+  if (int rc = fill_common(mesh, lset_v, fe_order, dt, intorder, &dd, &rv, &nv, &ri, &ni, 3)) return rc;
   ElvecArgs A{};
   if (int rc = fill_poly(h_f, A.f)) return rc;
   if (nlist == 0) return NGSX_OK;

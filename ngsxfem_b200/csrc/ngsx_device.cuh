@@ -178,11 +178,23 @@ __device__ __forceinline__ unsigned edge_orientation(const int *v) {
 
 // shape value of dof i at barycentrics lam
 template <int DIM, int ORDER>
-__device__ __forceinline__ double h1_shape(int i, const double *lam) {
+__device__ __forceinline__ double h1_shape(int i, const double *lam, unsigned orient = 0) {
   if (i <= DIM) return sel4(lam, i);
-  int a, b;
-  edge_vertices<DIM>(i - (DIM + 1), a, b);
-  return -0.5 * sel4(lam, a) * sel4(lam, b);
+  constexpr int NEDGE = H1<DIM, ORDER>::NEDGE;
+  constexpr int PER = ORDER == 3 ? 2 : 1;
+  const int r = i - (DIM + 1);
+  if (ORDER < 3 || r < PER * NEDGE) {
+    const int e = r / PER, k = r % PER;
+    int a, b;
+    edge_vertices<DIM>(e, a, b);
+    const double la = sel4(lam, a), lb = sel4(lam, b);
+    if (ORDER == 3 && k == 1) return -0.5 * (((orient >> e) & 1u) ? la - lb : lb - la) * (la * lb);
+    return -0.5 * la * lb;
+  }
+  const int f = r - PER * NEDGE;
+  int a = 0, b = 1, c = 2;
+  if (DIM == 3) { a = f == 3 ? 0 : 3; b = f == 0 ? 1 : (f == 1 ? 2 : (f == 2 ? 0 : 2)); c = f == 0 ? 2 : (f == 1 ? 0 : 1); }
+  return sel4(lam, a) * sel4(lam, b) * sel4(lam, c);
 }
 
 // shape value + gradient w.r.t. the coordinates in which gl[k][:] (gradients of the barycentrics) are given

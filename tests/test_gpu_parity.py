@@ -229,7 +229,7 @@ def test_linear_form_against_oracle(X):
     gf = X.ngs.GridFunction(X.ngs.H1(mesh, order=1))
     X.xfem.InterpolateToP1(X.ngs.SphereLevelset((0.5, 0.5, 0.5), 0.35), gf)
     x, y, z = X.ngs.x, X.ngs.y, X.ngs.z
-    for fo in (1, 2):
+    for fo in (1, 2, 3):                                         # order 3: orientation-dependent edge functions + face functions
         Vh = X.ngs.H1(mesh, order=fo)
         u, v = Vh.TnT()
         for dt in (NEG, IF):
