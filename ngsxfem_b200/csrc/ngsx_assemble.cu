@@ -92,7 +92,10 @@ __device__ __forceinline__ void bary_gradients(const ElGeom<DIM> &G, double (*gl
 template <int DIM, int ORDER, int SINK>
 __global__ void __launch_bounds__(WARPS * 32) k_elmat(ElmatArgs A, int64_t first, int64_t count) {
   using S = Smem<DIM, ORDER>;
-  constexpr int ND = S::ND, NE = S::NE, NPAIR = S::NPAIR, T = (NE + 31) / 32;
+  // order 3: the block is symmetric and never takes the constant-rule path -> lanes hold the lower triangle only (210 instead of 400
+  // entries of a P3 tet: 7 instead of 13 accumulators per lane), mirrored at the sink
+  constexpr bool SYM = ORDER == 3;
+  constexpr int ND = S::ND, NE = S::NE, NPAIR = S::NPAIR, NENT = SYM ? ND * (ND + 1) / 2 : NE, T = (NENT + 31) / 32;
   extern __shared__ __align__(16) unsigned char smem_raw[];
   double4 *srule_vol = reinterpret_cast<double4 *>(smem_raw + S::rule_vol());
   double4 *srule_if = reinterpret_cast<double4 *>(smem_raw + S::rule_if(A.nr_vol));
@@ -151,8 +154,15 @@ __global__ void __launch_bounds__(WARPS * 32) k_elmat(ElmatArgs A, int64_t first
 #pragma unroll
   for (int t = 0; t < T; t++) {
     int idx = lane + 32 * t;
-    ei[t] = idx < NE ? idx / ND : 0;
-    ej[t] = idx < NE ? idx % ND : 0;
+    if constexpr (SYM) {
+      int i = 0;
+      while ((i + 1) * (i + 2) / 2 <= idx) i++;
+      ei[t] = idx < NENT ? i : 0;
+      ej[t] = idx < NENT ? idx - i * (i + 1) / 2 : 0;
+    } else {
+      ei[t] = idx < NE ? idx / ND : 0;
+      ej[t] = idx < NE ? idx % ND : 0;
+    }
   }
 
   if (A.d_count) count = *A.d_count;
@@ -201,7 +211,7 @@ __global__ void __launch_bounds__(WARPS * 32) k_elmat(ElmatArgs A, int64_t first
 #pragma unroll
           for (int t = 0; t < T; t++) {
             int idx = lane + 32 * t;
-            if (idx < NE) {
+            if (!SYM && idx < NE) {
               double s = 0.0;
 #pragma unroll
               for (int q = 0; q < NPAIR; q++) s += gs[q] * tab[q * NE + idx];
@@ -288,7 +298,14 @@ __global__ void __launch_bounds__(WARPS * 32) k_elmat(ElmatArgs A, int64_t first
 #pragma unroll
         for (int t = 0; t < T; t++) {
           int idx = lane + 32 * t;
-          if (idx < NE) A.elmats[k * NE + idx] = acc[t];
+          if constexpr (SYM) {
+            if (idx < NENT) {
+              A.elmats[k * NE + ei[t] * ND + ej[t]] = acc[t];
+              if (ei[t] != ej[t]) A.elmats[k * NE + ej[t] * ND + ei[t]] = acc[t];
+            }
+          } else {
+            if (idx < NE) A.elmats[k * NE + idx] = acc[t];
+          }
         }
         if (A.npts && lane == 0) A.npts[k] = np_used;
       } else {
@@ -296,7 +313,12 @@ __global__ void __launch_bounds__(WARPS * 32) k_elmat(ElmatArgs A, int64_t first
 #pragma unroll
           for (int t = 0; t < T; t++) {
             int idx = lane + 32 * t;
-            if (idx < NE) {
+            if constexpr (SYM) {
+              if (idx < NENT) {                               // (i, j) and (j, i) are distinct CSR entries: no two lanes share a slot
+                A.vals[__ldg(A.slots + k * NE + ei[t] * ND + ej[t])] += acc[t];
+                if (ei[t] != ej[t]) A.vals[__ldg(A.slots + k * NE + ej[t] * ND + ei[t])] += acc[t];
+              }
+            } else if (idx < NE) {
               int32_t sl = __ldg(A.slots + k * NE + idx);
               A.vals[sl] += acc[t];
             }
