@@ -188,3 +188,52 @@ def test_dcut_symbols_build_the_same_integrators():
     assert [p[1].levelset_domain["domain_type"] for p in two.parts] == [xfem.NEG, xfem.POS]
     rhs = (1.0 + ngs.x) * v * xfem.dCut(None, xfem.IF)
     assert rhs.parts[0][0].poly.terms == {(0, 0, 0): 1.0, (1, 0, 0): 1.0}
+
+
+def test_deformation_host_logic():
+    """row f-4 host side (no GPU): mesh.SetDeformation validates the space (vector H1 of order 1..2 with dim = mesh.dim), the
+    ngsx_deformation struct has the C layout of include/ngsx_abi.h, integrators and differential symbols carry their deformation,
+    element blocks inherit the mesh's, and nothing reaches a kernel with host tensors"""
+    import ctypes
+    import pytest
+    from ngsxfem_b200 import _lib, meshes, ngs, xfem
+    from ngsxfem_b200.ngs import Expr
+    assert ctypes.sizeof(_lib.Deformation) == 32 and _lib.Deformation.el2dof.offset == 16 and _lib.Deformation.coef.offset == 24
+    mesh = ngs.Mesh(meshes.MakeStructured2DMesh(3), device="cpu")
+    gf = ngs.GridFunction(ngs.H1(mesh, order=1))
+    for bad in (gf, ngs.GridFunction(ngs.H1(mesh, order=3, dim=2)), ngs.GridFunction(ngs.H1(mesh, order=2, dim=3))):
+        with pytest.raises(_lib.NgsxError):
+            mesh.SetDeformation(bad)
+    defo = ngs.GridFunction(ngs.H1(mesh, order=2, dim=2))
+    assert tuple(defo.vec.shape) == (defo.space.ndof, 2)
+    mesh.SetDeformation(defo)
+    blk = mesh.element_block(2, 7)
+    assert blk.deformation is defo and blk._block == (2, 7)
+    with pytest.raises(_lib.NgsxError):                                    # host tensors never reach the library
+        mesh.c_deformation()
+    mesh.UnsetDeformation()
+    assert mesh.deformation is None and mesh.c_deformation() is None
+    u, v = Expr.atom("u"), Expr.atom("v")
+    bfi = xfem.SymbolicBFI(levelset_domain={"levelset": gf, "domain_type": xfem.NEG}, form=u * v, deformation=defo)
+    lfi = xfem.SymbolicLFI(levelset_domain={"levelset": gf, "domain_type": xfem.NEG}, form=1.0 * v, deformation=defo)
+    assert bfi.deformation is defo and lfi.deformation is defo
+    sym = xfem.dCut(gf, xfem.IF, deformation=defo)
+    assert sym.deformation is defo and sym(order=3).deformation is defo and xfem.dx(levelset_domain=sym.levelset_domain).deformation is None
+    a = xfem.BilinearForm(ngs.H1(mesh, order=2))
+    a += (u * v) * sym
+    assert a.integrators[0].deformation is defo and a._deformation_of(a.integrators[0]) is defo
+
+
+def test_weighted_element_blocks():
+    """sweep blocks of the multi-GPU step: contiguous, tiling, balanced by weight; degenerate inputs"""
+    import torch
+    from ngsxfem_b200 import partition
+    w = torch.ones(1000, dtype=torch.float64)
+    w[400:600] += 40.0
+    for world in (1, 2, 3, 8):
+        b = partition.element_blocks_weighted(w, world)
+        assert len(b) == world and b[0][0] == 0 and b[-1][1] == 1000 and all(b[r][1] == b[r + 1][0] for r in range(world - 1))
+        shares = [float(w[lo:hi].sum() / w.sum()) for lo, hi in b]
+        assert max(shares) <= 1.0 / world + 0.01
+    assert partition.element_blocks_weighted(torch.ones(3, dtype=torch.float64), 8)[-1][1] == 3
+    assert partition.element_blocks_weighted(torch.zeros(0, dtype=torch.float64), 2) == [(0, 0), (0, 0)]
