@@ -34,7 +34,7 @@ LocalHeap & GetLH()
 }
 
 
-int NV(ELEMENT_TYPE et) { return ngfem::Dim(et) + 1; }
+int NV(ELEMENT_TYPE et) { return ElementTopology::GetNVertices(et); }      // simplices: dim + 1; ET_QUAD 4, ET_HEX 8 (f-5 groundwork)
 
 int CopyRule(const IntegrationRule * ir, double * pts3, double * wts, int cap)
 {

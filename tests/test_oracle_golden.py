@@ -93,3 +93,57 @@ def test_small_mesh(golden_meshes, tag):
             scale = np.abs(gm).reshape(len(gm), -1).max(axis=1)
             err = np.abs(em - gm).reshape(len(gm), -1).max(axis=1)
             assert (err <= RTOL * np.maximum(scale, 1e-300)).all()
+
+
+# ---- SURVEY section 8 row f-5 (quad / hex cut rules): groundwork only -- no oracle restatement and no CUDA path yet ----------
+def _split(g, key):
+    n = g[key + "_n"]
+    off = np.concatenate([[0], np.cumsum(np.maximum(n, 0))])
+    return n, [(g[key + "_pts"][off[t]:off[t + 1]], g[key + "_wts"][off[t]:off[t + 1]]) for t in range(len(n))]
+
+
+@pytest.mark.parametrize("name,nv", [("quad", 4), ("hex", 8)])
+def test_quad_hex_golden_invariants(name, nv):
+    """the committed rules of the reference's LevelsetCutQuadrilateral (tests/golden/quad_hex_rules.npz, made by
+    tools/gen_golden.py from the compiled reference) are self-consistent: uncut elements carry the tensor rule in exactly one of
+    NEG / POS, cut elements split the unit square / cube (NEG + POS weights = 1 where the rule order integrates the split exactly),
+    points lie in the reference element, interface rules exist exactly on cut elements"""
+    import os
+    g = np.load(os.path.join(os.path.dirname(__file__), "golden", "quad_hex_rules.npz"))
+    ls = g[f"{name}_lset"]
+    assert ls.shape[1] == nv
+    for order in (1, 2, 4):
+        n0, r0 = _split(g, f"{name}_dt0_o{order}")
+        n1, r1 = _split(g, f"{name}_dt1_o{order}")
+        n2, r2 = _split(g, f"{name}_dt2_o{order}")
+        assert (n0 != -2).all() and (n1 != -2).all() and (n2 != -2).all()
+        for t in range(len(ls)):
+            haspos, hasneg = (ls[t] > 0).any(), (ls[t] < 0).any()
+            if not (haspos and hasneg):                                   # vertex values of one sign: the reference treats it as uncut
+                assert n2[t] == -1 and (n0[t] > 0) != (n1[t] > 0)
+                w = r0[t][1] if n0[t] > 0 else r1[t][1]
+                assert abs(w.sum() - 1.0) < 1e-13
+            else:
+                assert n2[t] > 0 and n0[t] > 0 and n1[t] > 0
+                assert abs(r0[t][1].sum() + r1[t][1].sum() - 1.0) < (1e-12 if order >= 2 else 0.2)
+            for n, r in ((n0, r0), (n1, r1), (n2, r2)):
+                if n[t] > 0:
+                    assert (r[t][0] > -1e-14).all() and (r[t][0] < 1 + 1e-14).all()
+
+
+def test_quad_hex_golden_matches_compiled_reference():
+    """regeneration check: the committed file is what the compiled reference produces today (skipped without oracle/_ref)"""
+    import importlib.util
+    import os
+    from oracle import refload
+    if not refload.available():
+        pytest.skip("oracle/_ref not built (needs /root/reference)")
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    spec = importlib.util.spec_from_file_location("gen_golden", os.path.join(root, "tools", "gen_golden.py"))
+    gg = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(gg)
+    fresh = gg.quad_hex_rules(only_return=True)
+    g = np.load(os.path.join(root, "tests", "golden", "quad_hex_rules.npz"))
+    assert set(fresh) == set(g.files)
+    for k in g.files:
+        assert fresh[k].shape == g[k].shape and np.array_equal(fresh[k], g[k]), k

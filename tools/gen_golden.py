@@ -108,8 +108,52 @@ def small_meshes():
     print("small_meshes.npz", len(out), "arrays")
 
 
+def ref_rule_et(et, ls, dt, order, cap=8192):
+    """StraightCutIntegrationRuleUntransformed of the compiled reference for any element type (ET_QUAD = 11, ET_HEX = 24)"""
+    import ctypes
+    dp = ctypes.POINTER(ctypes.c_double)
+    ls = np.ascontiguousarray(ls, dtype=np.float64); pts = np.zeros((cap, 3)); w = np.zeros(cap)
+    n = refload.load().ref_cut_rule_untrafo(et, ls.ctypes.data_as(dp), dt, order, pts.ctypes.data_as(dp), w.ctypes.data_as(dp), cap)
+    return n, pts[:max(n, 0)].copy(), w[:max(n, 0)].copy()
+
+
+def quad_hex_rules(only_return=False):
+    """SURVEY section 8 row f-5 groundwork (no CUDA path yet): cut rules of the reference's LevelsetCutQuadrilateral
+    (cutint/straightcutrule.cpp:206-501) on the reference square / cube for seeded multilinear level sets (vertex values in
+    NGSolve's vertex order), FIND_OPTIMAL policy -- the target a quad / hex kernel has to meet.  Ragged rules are stored flat
+    with offsets; n = -1: the reference returns no rule (element outside the domain), -2: it throws."""
+    rng = np.random.default_rng(SEED + 5)
+    out = {}
+    for name, et, nv, n in (("quad", 11, 4, 80), ("hex", 24, 8, 60)):
+        ls = rng.uniform(-1, 1, (n, nv))
+        for t in range(n):
+            if t % 8 == 1: ls[t] = np.abs(ls[t])
+            if t % 8 == 2: ls[t] = -np.abs(ls[t])
+            if t % 8 == 3: ls[t] = rng.uniform(-1, 1) + rng.uniform(-1, 1, 3)[:2 if nv == 4 else 3] @ (np.array(
+                [[0, 1, 1, 0], [0, 0, 1, 1]] if nv == 4 else [[0, 1, 1, 0, 0, 1, 1, 0], [0, 0, 1, 1, 0, 0, 1, 1], [0, 0, 0, 0, 1, 1, 1, 1]], dtype=float))   # affine
+            if t % 8 == 4: ls[t, rng.integers(nv)] = 1e-14
+        out[f"{name}_lset"] = ls
+        for dt in (0, 1, 2):
+            for order in (1, 2, 4):
+                cnt = np.zeros(n, dtype=np.int32); P = []; W = []
+                for t in range(n):
+                    k, p, w = ref_rule_et(et, ls[t], dt, order)
+                    cnt[t] = k
+                    if k > 0:
+                        P.append(p); W.append(w)
+                out[f"{name}_dt{dt}_o{order}_n"] = cnt
+                out[f"{name}_dt{dt}_o{order}_pts"] = np.concatenate(P) if P else np.zeros((0, 3))
+                out[f"{name}_dt{dt}_o{order}_wts"] = np.concatenate(W) if W else np.zeros(0)
+    if only_return:
+        return out
+    np.savez_compressed(os.path.join(OUT, "quad_hex_rules.npz"), **out)
+    print("quad_hex_rules.npz", len(out), "arrays")
+
+
 if __name__ == "__main__":
     assert refload.available(), "build oracle/_ref first (bash oracle/build_ref.sh)"
     os.makedirs(OUT, exist_ok=True)
-    single_elements()
-    small_meshes()
+    if "--quad-hex-only" not in sys.argv:
+        single_elements()
+        small_meshes()
+    quad_hex_rules()
