@@ -157,7 +157,7 @@ class FESpace:
 
 
 class H1(FESpace):
-    """H1HighOrderFESpace stand-in (orders 1..2 on the CUDA path)."""
+    """H1HighOrderFESpace stand-in (orders 1..2 on every entry point of the CUDA path, order 3 for bilinear / linear forms)."""
 
     def __init__(self, mesh: Mesh, order: int = 1, dgjumps: bool = False, dim: int = 1, **_):
         self.mesh, self.order, self.dgjumps, self.dim = mesh, order, dgjumps, dim          # dim > 1: interleaved vector field
