@@ -147,3 +147,30 @@ def test_quad_hex_golden_matches_compiled_reference():
     assert set(fresh) == set(g.files)
     for k in g.files:
         assert fresh[k].shape == g[k].shape and np.array_equal(fresh[k], g[k]), k
+
+
+def test_quad_restatement_against_golden():
+    """oracle/quad_ref.py (2D LevelsetCutQuadrilateral, FIND_OPTIMAL: direction choice, topology-change splitting, tensor rule
+    along xi with the interface scaling, fallback to two triangles) against the rules of the compiled reference: point counts
+    bit-exact, points to 1e-14, weights to 1e-12 relative (+ 1e-15 absolute: slivers of measure 1e-28 at clamped vertices)"""
+    import os
+    from oracle import quad_ref as qr
+    g = np.load(os.path.join(os.path.dirname(__file__), "golden", "quad_hex_rules.npz"))
+    ls = g["quad_lset"]
+    seen = set()
+    for dt in (0, 1, 2):
+        for order in (1, 2, 4):
+            n, rules = _split(g, f"quad_dt{dt}_o{order}")
+            for t in range(len(ls)):
+                k, p, w = qr.rule_untrafo(ls[t], dt, order)
+                assert k == n[t], (t, dt, order)
+                if k > 0:
+                    gp, gw = rules[t]
+                    assert np.abs(p - gp).max() <= 1e-14
+                    assert (np.abs(w - gw) <= 1e-12 * np.abs(gw) + 1e-15).all()
+            if dt == 0 and order == 2:                                     # the fixture exercises every branch of the direction choice
+                for t in range(len(ls)):
+                    if qr.check(ls[t]) == qr.IF:
+                        e = qr.exact_crit_bound_2d(qr.coeffs(ls[t]))
+                        seen.add("both" if max(e) < qr.C_BOUND else ("one" if min(e) < qr.C_BOUND else "fallback"))
+    assert seen == {"both", "one", "fallback"}
