@@ -174,3 +174,29 @@ def test_quad_restatement_against_golden():
                         e = qr.exact_crit_bound_2d(qr.coeffs(ls[t]))
                         seen.add("both" if max(e) < qr.C_BOUND else ("one" if min(e) < qr.C_BOUND else "fallback"))
     assert seen == {"both", "one", "fallback"}
+
+
+def test_hex_restatement_against_golden():
+    """oracle/quad_ref.py, D = 3 (sufficient direction criterion, X_Z / Y_Z swaps, splitting at topology changes, tensor rule whose
+    slices are cut quadrilaterals) against the compiled reference's rules.  The 3D fallback to six tetrahedra is restated but not
+    reachable with a finite gradient: it needs, for every direction d, a corner where g_d^2 >= 0.998 (max g_0^2 + max g_1^2 +
+    max g_2^2) -- 20 000 random level sets produce none -- so the fixture cannot exercise it."""
+    import os
+    from oracle import quad_ref as qr
+    g = np.load(os.path.join(os.path.dirname(__file__), "golden", "quad_hex_rules.npz"))
+    ls = g["hex_lset"]
+    for dt in (0, 1, 2):
+        for order in (1, 2, 4):
+            n, rules = _split(g, f"hex_dt{dt}_o{order}")
+            for t in range(len(ls)):
+                k, p, w = qr.rule_untrafo_hex(ls[t], dt, order)
+                assert k == n[t], (t, dt, order)
+                if k > 0:
+                    gp, gw = rules[t]
+                    assert np.abs(p - gp).max() <= 1e-13
+                    assert (np.abs(w - gw) <= 1e-11 * np.abs(gw) + 1e-15).all()
+    dirs = set()
+    for t in range(len(ls)):
+        if qr.check(ls[t]) == qr.IF:
+            dirs.add(int(np.argmin(qr.sufficient_crit_bound(qr.coeffs3(ls[t])))))
+    assert dirs == {0, 1, 2}
