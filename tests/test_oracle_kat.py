@@ -196,3 +196,41 @@ def test_deformed_similarity_and_zero_deformation(dim, dord):
         bub[m.nv:][inner_edge] = 0.05 * rng.uniform(-1, 1, (int(inner_edge.sum()), dim))
         tot = sum(orc.integrate_mesh_iso(dim, el2v, vert, ls, dord, e2d, bub, dt, 4, mono)[0] for dt in (NEG, POS))
         assert abs(tot - 1.0) <= 1e-12
+
+
+# ---- SURVEY section 8 row f-5 groundwork: the reference's quad / hex known answers on the restatement oracle/quad_ref.py ----------
+QUAD_V = [(0, 0), (1, 0), (1, 1), (0, 1)]
+HEX_V = [(0, 0, 0), (1, 0, 0), (1, 1, 0), (0, 1, 0), (0, 0, 1), (1, 0, 1), (1, 1, 1), (0, 1, 1)]
+
+
+@pytest.mark.parametrize("domain", [IF, NEG, POS])
+@pytest.mark.parametrize("dim", [0, 1])
+@pytest.mark.parametrize("eps", [1e-1, 1e-2, 5e-3, 1e-3, 0])
+def test_orth_cut_quad2d_epsiloned(domain, dim, eps):
+    # test_straightcutrule.py:128-157 with quads = True: one unit square, levelset 1 - 2 x + eps (y - 1/2) (or x <-> y), order 2
+    from oracle import quad_ref as qr
+    f = (lambda x, y: 1 - 2 * x + eps * (y - 0.5)) if dim == 0 else (lambda x, y: 1 - 2 * y + eps * (x - 0.5))
+    vals = p1(f, np.array(QUAD_V, dtype=float))
+    n, _, w = qr.rule_untrafo(vals, domain, 2)
+    ref = {NEG: 0.5, POS: 0.5, IF: sqrt(1.0 + eps * eps / 4)}[domain]
+    assert n > 0 and abs(w.sum() - ref) < 5e-15 * 9
+
+
+@pytest.mark.parametrize("domain", [NEG, POS, IF])
+@pytest.mark.parametrize("dim", [0, 1])
+def test_orth_cut_quad2d(domain, dim):
+    # test_straightcutrule.py:242-262 with quads = True: levelset 1 - 3 x (or y)
+    from oracle import quad_ref as qr
+    vals = p1((lambda x, y: 1 - 3 * x) if dim == 0 else (lambda x, y: 1 - 3 * y), np.array(QUAD_V, dtype=float))
+    n, _, w = qr.rule_untrafo(vals, domain, 2)
+    assert n > 0 and abs(w.sum() - {NEG: 2 / 3, POS: 1 / 3, IF: 1.0}[domain]) < 5e-15 * 9
+
+
+@pytest.mark.parametrize("domain", [NEG, POS, IF])
+@pytest.mark.parametrize("dim", [0, 1, 2])
+def test_orth_cut_hex3d(domain, dim):
+    # test_straightcutrule.py:265-285 with hexes = True: levelset 1 - 2 x (y, z) on one unit cube
+    from oracle import quad_ref as qr
+    vals = p1(lambda x, y, z: 1 - 2 * (x, y, z)[dim], np.array(HEX_V, dtype=float))
+    n, _, w = qr.rule_untrafo_hex(vals, domain, 2)
+    assert n > 0 and abs(w.sum() - {NEG: 0.5, POS: 0.5, IF: 1.0}[domain]) < 5e-15 * 9
