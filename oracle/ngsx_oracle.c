@@ -732,6 +732,172 @@ int64_t orc_elmat_mesh_iso(int dim, int64_t nel, const int64_t *els, const int32
   return nn;
 }
 
+/* ------------------------------------------------------------------ quadrilaterals (groundwork; 2D) */
+/* LevelsetCutQuadrilateral (cutint/straightcutrule.cpp:206-501), policy FIND_OPTIMAL, on the reference square for a bilinear level
+ * set given by its vertex values at (0,0), (1,0), (1,1), (0,1).  C twin of oracle/quad_ref.py (which also covers hexahedra); both
+ * are pinned against tests/golden/quad_hex_rules.npz (rules of the compiled reference). */
+typedef struct { double c00, c10, c01, c11; } qls_t;          /* LevelsetWrapper::GetCoeffsFromVals ET_QUAD (:512-514) */
+static double qls(const qls_t *c, double x, double y) { return c->c00 + c->c10*x + c->c01*y + c->c11*x*y; }
+static int qcheck(int n, const double *v, double eps)         /* CheckIfStraightCut (:11-39) */
+{
+  int hp = 0, hn = 0;
+  for (int i = 0; i < n; i++) { if (v[i] > eps) hp = 1; if (v[i] < -eps) hn = 1; }
+  if (hp == hn) return IF;
+  return hn ? NEG : POS;
+}
+typedef struct { double *p, *w; int n, cap, err; } qout_t;
+static void qpush(qout_t *o, double x, double y, double w)
+{
+  if (o->n >= o->cap) { o->err = ORC_CAP; return; }
+  o->p[3*o->n] = x; o->p[3*o->n + 1] = y; o->p[3*o->n + 2] = 0.0; o->w[o->n] = w; o->n++;
+}
+/* Quadrilateral::GetPlainIntegrationRule (:102-128): tensor Gauss rule, x outer, y inner */
+static void qplain(double x0, double x1, double y0, double y1, int order, qout_t *o)
+{
+  const double (*r)[4];
+  int n = select_rule(1, order, &r);
+  double vol = fabs((x1 - x0) * (y1 - y0));
+  for (int i = 0; i < n; i++)
+    for (int j = 0; j < n; j++) qpush(o, x0 + (x1 - x0)*r[i][0], y0 + (y1 - y0)*r[j][0], r[i][3]*r[j][3]*vol);
+}
+/* GetTensorProductAlongXiIntegrationRule (:255-303), D = 2 */
+static void qtensor(const qls_t *c, int dt, double x0, double x1, double y0, double y1, int order, qout_t *o)
+{
+  const double (*r)[4];
+  int n = select_rule(1, order, &r);
+  for (int i = 0; i < n; i++) {
+    double ya = y0 + r[i][0]*(y1 - y0);
+    double proj[2] = { qls(c, x1, ya), qls(c, x0, ya) };          /* ET_SEGM vertex 0 sits at xhat = 1 */
+    if (qcheck(2, proj, 0.0) != IF || proj[0] == 0.0 || proj[1] == 0.0) { o->err = ORC_THROW; return; }
+    double p2[3*64], w2[64];
+    int k = orc_cut_rule_untrafo(1, proj, dt, order, p2, w2, 64);
+    for (int q = 0; q < k; q++) {
+      double x = x0 + p2[3*q]*(x1 - x0), sc = 1.0;
+      if (dt == IF) {
+        double gx = c->c10 + c->c11*ya, gy = c->c01 + c->c11*x;
+        sc = sqrt(gx*gx + gy*gy) / fabs(gx);
+      }
+      qpush(o, x, ya, w2[q]*r[i][3]*(y1 - y0)*sc);
+    }
+  }
+}
+/* GetIntegrationRuleAlongXi (:453-468) with HasTopologyChangeAlongXi (:206-218) and Decompose (:220-251) on the unit square */
+static void qalong(const qls_t *c, int dt, int order, qout_t *o)
+{
+  double v[4] = { qls(c, 0, 0), qls(c, 1, 0), qls(c, 1, 1), qls(c, 0, 1) };
+  int d = qcheck(4, v, 0.0);
+  if (d != IF) { if (d == dt) qplain(0, 1, 0, 1, order, o); return; }
+  double xs[4] = { 0.0, 1.0, 0, 0 };
+  int nx = 2;
+  const int ea[2] = { 1, 0 }, eb[2] = { 2, 3 };
+  for (int e = 0; e < 2; e++) {
+    double ev[2] = { v[eb[e]], v[ea[e]] };
+    if (qcheck(2, ev, 0.0) == IF) {
+      double xi = 1.0 + ev[0] / (ev[0] - ev[1]) * (0.0 - 1.0);
+      int dup = 0;
+      for (int k = 0; k < nx; k++) if (xs[k] == xi) dup = 1;
+      if (!dup) xs[nx++] = xi;
+    }
+  }
+  if (nx == 2) { qtensor(c, dt, 0, 1, 0, 1, order, o); return; }
+  for (int a = 0; a < nx; a++) for (int b = a + 1; b < nx; b++) if (xs[b] < xs[a]) { double t = xs[a]; xs[a] = xs[b]; xs[b] = t; }
+  for (int k = 0; k + 1 < nx; k++) {
+    double sv[4] = { qls(c, 0, xs[k]), qls(c, 1, xs[k]), qls(c, 1, xs[k+1]), qls(c, 0, xs[k+1]) };
+    int d2 = qcheck(4, sv, 1e-15);
+    if (d2 == IF) qtensor(c, dt, 0, 1, xs[k], xs[k+1], order, o);
+    else if (d2 == dt) qplain(0, 1, xs[k], xs[k+1], order, o);
+  }
+}
+/* GetFallbackIntegrationRule (:470-489): triangles {0,1,3}, {2,1,3}, level set re-interpolated at their vertices (clamped) */
+static void qfallback(const qls_t *c, int dt, int order, qout_t *o)
+{
+  static const double CR[4][2] = { {0,0}, {1,0}, {1,1}, {0,1} };
+  static const int TRI[2][3] = { {0,1,3}, {2,1,3} };
+  for (int t = 0; t < 2; t++) {
+    double P[3][2], v[3];
+    for (int k = 0; k < 3; k++) {
+      P[k][0] = CR[TRI[t][k]][0]; P[k][1] = CR[TRI[t][k]][1];
+      double d = qls(c, P[k][0], P[k][1]);
+      v[k] = fabs(d) > 1e-14 ? d : 1e-14;                           /* LevelsetWrapper::update_initial_coefs (:547-556) */
+    }
+    int d = qcheck(3, v, 0.0);
+    if (d != IF && d == dt) {                                       /* SimpleX::GetPlainIntegrationRule (:80-100), base point p0 */
+      const double (*r)[4];
+      int n = select_rule(2, order, &r);
+      double det = fabs((P[1][0]-P[0][0])*(P[2][1]-P[0][1]) - (P[2][0]-P[0][0])*(P[1][1]-P[0][1]));
+      for (int q = 0; q < n; q++) {
+        double l0 = 1.0 - r[q][0] - r[q][1];
+        qpush(o, l0*P[0][0] + r[q][0]*P[1][0] + r[q][1]*P[2][0], l0*P[0][1] + r[q][0]*P[1][1] + r[q][1]*P[2][1], r[q][3]*det);
+      }
+    } else if (d == IF && dt != IF) {                               /* volumes: affine image of the reference-triangle cut rule */
+      double p2[3*256], w2[256];
+      int n = orc_cut_rule_untrafo(2, v, dt, order, p2, w2, 256);
+      if (n == ORC_THROW) { o->err = ORC_THROW; return; }
+      double det = fabs((P[0][0]-P[2][0])*(P[1][1]-P[2][1]) - (P[1][0]-P[2][0])*(P[0][1]-P[2][1]));
+      for (int q = 0; q < n; q++) {
+        double a = p2[3*q], b = p2[3*q+1], l2 = 1.0 - a - b;
+        qpush(o, a*P[0][0] + b*P[1][0] + l2*P[2][0], a*P[0][1] + b*P[1][1] + l2*P[2][1], w2[q]*det);
+      }
+    } else if (d == IF) {                                           /* interface: one segment between the two edge zeros */
+      double cut[3][2];
+      int nc = 0;
+      for (int i = 0; i < 3; i++)
+        for (int j = i + 1; j < 3; j++)
+          if ((v[i] >= 0) != (v[j] >= 0)) {
+            double f = v[i] / (v[i] - v[j]);
+            cut[nc][0] = P[i][0] + f*(P[j][0] - P[i][0]); cut[nc][1] = P[i][1] + f*(P[j][1] - P[i][1]); nc++;
+          }
+      if (nc != 2) { o->err = ORC_THROW; return; }
+      const double (*r)[4];
+      int n = select_rule(1, order, &r);
+      double len = sqrt((cut[1][0]-cut[0][0])*(cut[1][0]-cut[0][0]) + (cut[1][1]-cut[0][1])*(cut[1][1]-cut[0][1]));
+      for (int q = 0; q < n; q++)
+        qpush(o, (1.0 - r[q][0])*cut[0][0] + r[q][0]*cut[1][0], (1.0 - r[q][0])*cut[0][1] + r[q][0]*cut[1][1], r[q][3]*len);
+    }
+  }
+}
+/* StraightCutIntegrationRuleUntransformed for ET_QUAD (:663-726) + GetIntegrationRule / GetDimensionSwap (:415-434, :491-500) */
+int orc_quad_rule_untrafo(const double *vals, int dt, int order, double *pts3, double *wts, int cap)
+{
+  qout_t o = { pts3, wts, 0, cap, 0 };
+  int d = qcheck(4, vals, 0.0);
+  if (d != IF) {
+    if (d != dt) return ORC_NULL;
+    qplain(0, 1, 0, 1, order, &o);
+    return o.err ? o.err : o.n;
+  }
+  qls_t c;
+  c.c00 = vals[0]; c.c10 = vals[1] - c.c00; c.c01 = vals[3] - c.c00; c.c11 = vals[2] - c.c10 - c.c01 - c.c00;
+  /* GetExactCritsQBound2D (:392-413) */
+  int allow[2] = { 1, 1 };
+  double h = -c.c10 / c.c11;
+  if (h > 0 && h < 1) allow[1] = 0;
+  h = -c.c01 / c.c11;
+  if (h > 0 && h < 1) allow[0] = 0;
+  double qm[2] = { 0, 0 };
+  static const double CR[4][2] = { {0,0}, {1,0}, {1,1}, {0,1} };
+  for (int k = 0; k < 4; k++) {
+    double gx = c.c10 + c.c11*CR[k][1], gy = c.c01 + c.c11*CR[k][0], nr = sqrt(gx*gx + gy*gy);
+    double qy = fabs(gy)/nr, qx = fabs(gx)/nr;
+    if (qy > qm[1]) qm[1] = qy;
+    if (qx > qm[0]) qm[0] = qx;
+  }
+  for (int k = 0; k < 2; k++) if (!allow[k]) qm[k] = 2.0;
+  const double cb = 0.999;
+  int sw;                                                           /* 0 ID, 1 X_Y, 2 NONE */
+  if (qm[0] < cb && qm[1] < cb) sw = qm[1] <= qm[0] ? 0 : 1;
+  else if (qm[1] < cb) sw = 0;
+  else if (qm[0] < cb) sw = 1;
+  else sw = 2;
+  if (sw == 0) qalong(&c, dt, order, &o);
+  else if (sw == 1) {                                               /* GetIntegrationRuleOnXYPermutatedQuad (:305-320) */
+    qls_t cr = { c.c00, c.c01, c.c10, c.c11 };
+    qalong(&cr, dt, order, &o);
+    for (int k = 0; k < o.n; k++) { double t = pts3[3*k]; pts3[3*k] = pts3[3*k+1]; pts3[3*k+1] = t; }
+  } else qfallback(&c, dt, order, &o);
+  return o.err ? o.err : o.n;
+}
+
 /* ------------------------------------------------------------------ mesh-level loops */
 static void gather_el(int dim, const int32_t *el2v, const double *vert, const double *lset_v, int64_t e, double *pmat, double *ls, int *vn)
 {

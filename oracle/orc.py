@@ -74,6 +74,7 @@ def load():
     L.orc_integrate_mesh_iso.restype = c_double
     L.orc_elmat_mesh_iso.argtypes = [c_int, c_i64, lp, ip, dp, dp, c_int, ip, dp, c_int, c_int, c_int, dp, dp, ip]
     L.orc_elmat_mesh_iso.restype = c_i64
+    L.orc_quad_rule_untrafo.argtypes = [dp, c_int, c_int, dp, dp, c_int]
     L.orc_set_threads.argtypes = [c_int]
     _LIB = L
     return L
@@ -392,3 +393,10 @@ def elvec_mesh_iso(dim, el2v, vert, lset_v, dord, el2dof_def, defo, fe_order, dt
     out = np.zeros((nel, nd)); npts = np.zeros(nel, dtype=np.int32)
     load().orc_elvec_mesh_iso(dim, nel, ep, P(ev, ip), P(vt), P(ls), dord, P(ed, ip), P(df), fe_order, dt, intorder, len(mo), P(mo), P(out), P(npts, ip))
     return out, npts
+
+
+def quad_rule_untrafo(vals, dt, order, cap=4096):
+    """cut rule on the reference quadrilateral (C twin of oracle/quad_ref.py:rule_untrafo)"""
+    v = _d(vals); pts = np.zeros((cap, 3)); w = np.zeros(cap)
+    n = load().orc_quad_rule_untrafo(P(v), dt, order, P(pts), P(w), cap)
+    return n, pts[:max(n, 0)], w[:max(n, 0)]

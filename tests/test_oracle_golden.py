@@ -200,3 +200,30 @@ def test_hex_restatement_against_golden():
         if qr.check(ls[t]) == qr.IF:
             dirs.add(int(np.argmin(qr.sufficient_crit_bound(qr.coeffs3(ls[t])))))
     assert dirs == {0, 1, 2}
+
+
+def test_quad_c_oracle_against_golden_and_python():
+    """orc_quad_rule_untrafo (the C twin in oracle/ngsx_oracle.c) against the compiled reference's goldens, and against the Python
+    restatement on 2 000 random bilinear level sets (order 3: not a golden order)"""
+    import os
+    from oracle import quad_ref as qr
+    g = np.load(os.path.join(os.path.dirname(__file__), "golden", "quad_hex_rules.npz"))
+    ls = g["quad_lset"]
+    for dt in (0, 1, 2):
+        for order in (1, 2, 4):
+            n, rules = _split(g, f"quad_dt{dt}_o{order}")
+            for t in range(len(ls)):
+                k, p, w = orc.quad_rule_untrafo(ls[t], dt, order)
+                assert k == n[t], (t, dt, order)
+                if k > 0:
+                    gp, gw = rules[t]
+                    assert np.abs(p - gp).max() <= 1e-14
+                    assert (np.abs(w - gw) <= 1e-12 * np.abs(gw) + 1e-15).all()
+    rng = np.random.default_rng(3)
+    for _ in range(2000):
+        v = rng.uniform(-1, 1, 4)
+        for dt in (0, 1, 2):
+            a, b = orc.quad_rule_untrafo(v, dt, 3), qr.rule_untrafo(v, dt, 3)
+            assert a[0] == b[0]
+            if a[0] > 0:
+                assert np.abs(a[1] - b[1]).max() <= 1e-13 and np.abs(a[2] - b[2]).max() <= 1e-13
