@@ -37,7 +37,7 @@ def parse():
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--nx", type=int, default=119)
     ap.add_argument("--group", type=int, default=6)
-    ap.add_argument("--cpu-seconds", type=float, default=12.0, help="target CPU time of the cpu_baseline sample")
+    ap.add_argument("--cpu-seconds", type=float, default=30.0, help="upper bound for one step of the CPU reference (larger workloads are sampled)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     return ap.parse_args()
 
@@ -298,6 +298,8 @@ def run_b200(args):
         main.wait_stream(comm)
     t_end.record()
     barrier()
+    if world == 1:
+        P["s_if"], P["s_neg"] = float(s_if.item()), float(s_neg.item())          # for the parity record (after the timed region)
     launches = launches_per_replay * args.steps if graph is not None else L.ngsx_launch_count() - launches0
     if graph is not None:                                # per-stage / per-kernel times of a graph run: eager serial steps after the timed region
         L.ngsx_debug_set_timing(1)
@@ -442,8 +444,7 @@ def run_b200(args):
         "metric": METRIC, "value": value, "unit": "elements/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
         "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f64",
         "data": "synthetic",
-        "config": {"workload": f"configs[1]: 3D unit-cube Kuhn tets nx={args.nx} ({mesh.ne} tets), sphere r=0.35, P2 H1, NEG grad-grad+mass "
-                               f"assemble-to-CSR ({n_global} HASNEG elements) + CutInfo + Integrate(IF,NEG)",
+        "config": {"workload": workload_name(args.nx, mesh.ne, n_global),
                    "ne": mesh.ne, "hasneg_elements": n_global, "nnz": nnz_global, "assembly": a.assembly, "group": args.group, "colors": plan.ncolors,
                    "setup_s_untimed": round(setup_s, 2), "stage_ms": {"classify": cl_ms, "assemble": as_ms, "integrate": in_ms},
                    "stage_ms_one_stream": serial_break, "launch": graph_note,
@@ -469,81 +470,173 @@ def run_b200(args):
                 "note": "mesh, dof table, sparsity and row plan stay resident; per step the level set is uploaded and the CSR values + integrals are downloaded; double-buffered: the download of step k overlaps the compute of step k+1, the timed region ends when the last download has landed"},
         "gpu_launches": int(launches_global), "clocks": clocks,
     }
+    parity_failed = False
     if world == 1 and not args.no_cpu_baseline:
         try:
-            out["cpu_baseline"] = cpu_baseline(P, args.cpu_seconds, steps=1, warmup=0)[0]
+            out["cpu_baseline"], out["parity"] = cpu_baseline_and_parity(P, args.cpu_seconds)
+            parity_failed = out["parity"].get("ok") is False
         except Exception as exc:                        # never lose the GPU line to a host-side problem
-            out["cpu_baseline"] = {"error": str(exc)[:200]}
+            out["cpu_baseline"] = {"error": f"{type(exc).__name__}: {str(exc)[:200]}"}
     print(json.dumps(out), flush=True)
     if world > 1:
         dist.destroy_process_group()
+    if parity_failed:
+        raise SystemExit("bench.py: the device results differ from the compiled reference beyond 1e-12 (see 'parity' in the JSON line)")
 
 
 # ======================================================================================================================
-def cpu_baseline(P, target_seconds, steps, warmup):
-    """the reference's own CPU code (oracle/_ref: straightcutrule.cpp + NGSolve FE/AddABt compiled in place) or, where that
-    library is absent, the C port (oracle/), on a bounded sample of the same workload: every k-th HASNEG element, all host
-    threads, colour by colour like NGSolve's IterateElements, scattered into the same CSR pattern."""
+# CPU arm: the reference's own code (oracle/_ref) on the host cores.  numpy + ctypes only -- no torch, no CUDA, no product
+# library, so the arm runs on a GPU-less host and `native_so_loaded` lists the reference library alone.
+# ======================================================================================================================
+def workload_name(nx, ne, n_hasneg):
+    return (f"configs[1]: 3D unit-cube Kuhn tets nx={nx} ({ne} tets), sphere r=0.35, P2 H1; step = CutInfo.Update (all elements) + NEG "
+            f"grad-grad+mass assemble-to-CSR ({n_hasneg} HASNEG elements) + Integrate(IF) + Integrate(NEG), order-4 rules")
+
+
+class ReferenceProblem:
+    """config 2 on the host: mesh, level set, P2 dof table (oracle/hostmesh.py or arrays handed in), HASNEG list, CSR pattern
+    and a greedy element colouring (oracle C helpers); the timed step calls the compiled reference only."""
+
+    def __init__(self, nx, arrays=None, pattern=None):
+        import numpy as np
+        from oracle import hostmesh, orc, refload
+        self.np, self.orc = np, orc
+        self.kind = "reference" if refload.available() else "port"
+        self.impl = "ref" if self.kind == "reference" else "oracle"
+        self.cores = os.cpu_count() or 1
+        H = hostmesh.config2(nx) if arrays is None else arrays
+        self.vert, self.el2v, self.ls, self.e2d, self.ndof = H["vert"], H["el2v"], H["ls"], H["el2dof"], H["ndof"]
+        self.ne = self.el2v.shape[0]
+        dom, _, nerr = orc.cutinfo_mesh(3, self.el2v, self.vert, self.ls, impl=self.impl, nthreads=self.cores)
+        if nerr:
+            raise RuntimeError(f"{nerr} degenerate elements")
+        self.active = np.nonzero(dom != orc.POS)[0]
+        table = self.e2d[self.active]
+        self.rowptr, self.colidx = pattern if pattern is not None else hostmesh.csr_pattern(table, self.ndof)
+        perm, self.cptr = hostmesh.color_elements(table, self.ndof)
+        self.els = self.active[perm].astype(np.int32)
+        self.pos_in_color = perm
+
+    def step(self, stride=1):
+        """one pass of the step over every stride-th element; returns (stage seconds, results)"""
+        np, orc = self.np, self.orc
+        el2v = self.el2v if stride == 1 else np.ascontiguousarray(self.el2v[::stride])
+        if stride == 1:
+            els, cptr = self.els, self.cptr
+        else:                                                # every stride-th HASNEG element, colours kept
+            keep = self.pos_in_color % stride == 0
+            els = self.els[keep]
+            cptr = np.concatenate([[0], np.cumsum([keep[self.cptr[c]:self.cptr[c + 1]].sum() for c in range(len(self.cptr) - 1)])]).astype(np.int64)
+        t = [time.perf_counter()]
+        dom, ratio, _ = orc.cutinfo_mesh(3, el2v, self.vert, self.ls, impl=self.impl, nthreads=self.cores)
+        t.append(time.perf_counter())
+        vals, nass = orc.assemble_csr(3, self.el2v, self.vert, self.ls, 2, self.e2d, 0, 4, 1.0, 1.0, cptr, els, self.rowptr, self.colidx,
+                                      impl=self.impl, nthreads=self.cores)
+        t.append(time.perf_counter())
+        s_if, _ = orc.integrate_mesh(3, el2v, self.vert, self.ls, 2, 4, impl=self.impl, nthreads=self.cores)
+        t.append(time.perf_counter())
+        s_neg, _ = orc.integrate_mesh(3, el2v, self.vert, self.ls, 0, 4, impl=self.impl, nthreads=self.cores)
+        t.append(time.perf_counter())
+        secs = {"classify": t[1] - t[0], "assemble": t[2] - t[1], "integrate": t[4] - t[2], "step": t[4] - t[0]}
+        return secs, dict(dom=dom, ratio=ratio, vals=vals, nass=nass, s_if=s_if, s_neg=s_neg, n_classified=el2v.shape[0])
+
+    def stride_for(self, target_seconds):
+        """bounded sample: the stride that brings one step to about target_seconds (1 = the whole workload)"""
+        probe = max(1, self.ne // 200000)
+        secs, _ = self.step(probe)
+        full = secs["step"] * probe
+        return max(1, int(full / max(target_seconds, 1e-3) + 0.999)), full
+
+    def info(self, secs_list, res, stride):
+        n = len(secs_list)
+        mean = {k: sum(s[k] for s in secs_list) / n for k in secs_list[0]}
+        nass, ncls = res["nass"], res["n_classified"]
+        return {"value": nass / mean["step"], "unit": "elements/s", "cores": self.cores, "kind": self.kind,
+                "sample": (f"every {stride}-th element of the workload" if stride > 1 else "the whole workload") +
+                          f" ({ncls} elements classified and integrated twice, {nass} HASNEG elements assembled; {mean['step']:.2f} s per step): "
+                          "reference StraightCutIntegrationRule + H1HighOrderFE + AddABt + AddElementMatrix row search under a per-element "
+                          "colouring, OpenMP threads = cores",
+                "stage_s": mean,
+                "stage_rates": {"classify_elements_per_s": ncls / mean["classify"], "assemble_elements_per_s": nass / mean["assemble"],
+                                "integrate_elements_per_s": 2 * ncls / mean["integrate"]}}, mean["step"] * 1e3
+
+
+def parity_record(got, ref, rowptr, rtol=1e-12):
+    """GPU results against the compiled reference on the same inputs at full size: flags bit-exact, cut ratios, CSR values
+    row-scaled and entrywise, integrals ('parity gates run in the same job')"""
     import numpy as np
-    import torch
-    from oracle import orc, refload
-    kind = "reference" if refload.available() else "port"
-    impl = "ref" if kind == "reference" else "oracle"
-    mesh, a, Vh, lsetp1 = P["mesh"], P["a"], P["Vh"], P["lsetp1"]
-    if a.mat is None:
-        a.Assemble()
-    el2v, vert, ls = mesh.el2v.cpu().numpy(), mesh.vert.cpu().numpy(), lsetp1.vec.cpu().numpy()
-    e2d = Vh.el2dof.cpu().numpy()
+    rec = {}
+    rec["flags_mismatch"] = int(np.count_nonzero(got["dom"] != ref["dom"]))
+    rec["elements_classified"] = int(len(ref["dom"]))
+    cut = ref["dom"] == 2
+    rec["cut_ratio_max_abs_diff"] = float(np.abs(got["ratio"][cut] - ref["ratio"][cut]).max()) if cut.any() else 0.0
+    d = np.abs(got["vals"] - ref["vals"])
+    a = np.abs(ref["vals"])
+    rowlen = np.diff(rowptr)
+    nz = rowlen > 0
+    starts = rowptr[:-1][nz]
+    rowmax = np.maximum.reduceat(a, starts) if len(starts) else np.zeros(0)
+    rowerr = np.maximum.reduceat(d, starts) if len(starts) else np.zeros(0)
+    ok = rowmax > 0
+    rec["csr_entries"] = int(len(a))
+    rec["csr_row_scaled_max_rel"] = float((rowerr[ok] / rowmax[ok]).max()) if ok.any() else 0.0
+    scale = np.repeat(rowmax, rowlen[nz])
+    sig = a >= 1e-3 * scale                                       # entries that are not cancellation residue of their row
+    rec["csr_entrywise_max_rel_significant"] = float((d[sig] / a[sig]).max()) if sig.any() else 0.0
+    rec["csr_entrywise_significant_entries"] = int(sig.sum())
+    rec["csr_global_max_rel"] = float(d.max() / a.max())
+    rec["integral_if_rel"] = abs(got["s_if"] - ref["s_if"]) / abs(ref["s_if"])
+    rec["integral_neg_rel"] = abs(got["s_neg"] - ref["s_neg"]) / abs(ref["s_neg"])
+    rec["rtol"] = rtol
+    rec["ok"] = bool(rec["flags_mismatch"] == 0 and rec["cut_ratio_max_abs_diff"] <= rtol and rec["csr_row_scaled_max_rel"] <= rtol and
+                     rec["csr_entrywise_max_rel_significant"] <= rtol and rec["integral_if_rel"] <= rtol and rec["integral_neg_rel"] <= rtol)
+    return rec
+
+
+def cpu_baseline_and_parity(P, target_seconds):
+    """rank 0, N = 1: one step of the compiled reference on the device's own inputs (downloaded), timed as the cpu_baseline
+    and compared with the device results as the parity record."""
+    import numpy as np
+    mesh, a, Vh, lsetp1, ci = P["mesh"], P["a"], P["Vh"], P["lsetp1"], P["ci"]
+    arrays = dict(vert=mesh.vert.cpu().numpy(), el2v=mesh.el2v.cpu().numpy(), ls=lsetp1.vec.cpu().numpy(),
+                  el2dof=Vh.el2dof.cpu().numpy(), ndof=Vh.ndof)
     rowptr, colidx = a.mat.rowptr.cpu().numpy(), a.mat.colidx.cpu().numpy()
-    active = a._plans[0].els.cpu().numpy() if 0 in a._plans else None
-    active = np.sort(active)
-    cores = os.cpu_count() or 1
-
-    def run(sample):
-        from ngsxfem_b200 import xfem
-        tab = torch.as_tensor(e2d[sample]).contiguous()
-        perm, cptr = xfem.color_list(tab, Vh.ndof, 1)                 # per-element colouring (NGSolve's)
-        els = sample[perm.numpy()].astype(np.int32)
-        t0 = time.perf_counter()
-        _, nass = orc.assemble_csr(3, el2v, vert, ls, 2, e2d, 0, 4, 1.0, 1.0, np.array(cptr, dtype=np.int64), els, rowptr, colidx,
-                                   impl=impl, nthreads=cores)
-        return time.perf_counter() - t0, nass
-
-    probe = active[:: max(1, len(active) // 20000)]
-    dt, n = run(probe)
-    rate = n / dt
-    nsample = int(min(len(active), max(20000, rate * target_seconds)))
-    sample = active[:: max(1, len(active) // nsample)]
-    res = []
-    for i in range(warmup + steps):
-        dt, n = run(sample)
-        if i >= warmup:
-            res.append((dt, n))
-    tot_t = sum(r[0] for r in res); tot_n = sum(r[1] for r in res)
-    info = {"value": tot_n / tot_t, "unit": "elements/s", "cores": cores, "kind": kind,
-            "sample": f"every {max(1, len(active) // nsample)}-th of the {len(active)} HASNEG elements ({len(sample)} elements, {tot_t / len(res):.1f} s per pass), "
-                      f"rule + P2 element matrix + CSR scatter under a per-element colouring, OpenMP threads = cores"}
-    return info, tot_t / len(res) * 1e3
+    R = ReferenceProblem(0, arrays, pattern=(rowptr, colidx))
+    stride, full = R.stride_for(target_seconds)
+    secs, res = R.step(stride)
+    info, _ = R.info([secs], res, stride)
+    parity = None
+    if stride == 1:
+        got = dict(dom=ci.dom.cpu().numpy(), ratio=ci.ratio.cpu().numpy(), vals=a.mat.vals.cpu().numpy(),
+                   s_if=P["s_if"], s_neg=P["s_neg"])
+        parity = parity_record(got, res, rowptr)
+    else:
+        parity = {"ok": None, "note": f"reference step estimated at {full:.0f} s > --cpu-seconds: sampled, no full-size comparison"}
+    return info, parity
 
 
 def run_reference(args):
     rank = int(os.environ.get("RANK", 0))
     if rank != 0:
         return
-    import torch
     import __graft_entry__ as ge
-    ge.build()
-    dev = "cuda:0" if torch.cuda.is_available() else "cpu"
-    if dev == "cpu":
-        raise SystemExit("reference arm: mesh/sparsity setup uses the product's device builders; needs the GPU box")
-    P = build_problem(args.nx, dev, 0, 1, args.group)
-    P["a"].Assemble()
-    info, ms = cpu_baseline(P, args.cpu_seconds, steps=args.steps, warmup=args.warmup)
+    ge.build_oracle()
+    R = ReferenceProblem(args.nx)
+    stride, _ = R.stride_for(min(args.cpu_seconds, 200.0 / (args.steps + args.warmup)))       # whole run within a few minutes
+    secs = []
+    res = None
+    for i in range(args.warmup + args.steps):
+        s, res = R.step(stride)
+        if i >= args.warmup:
+            secs.append(s)
+    info, ms = R.info(secs, res, stride)
     out = {"impl": "reference", "metric": METRIC, "value": info["value"], "unit": "elements/s", "n_gpus": args.gpus, "steps": args.steps,
            "warmup": args.warmup, "ms_per_step": ms, "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f64",
            "data": "synthetic",
-           "config": {"workload": f"configs[1]: 3D unit-cube Kuhn tets nx={args.nx}, sphere r=0.35, P2 H1, NEG grad-grad+mass assemble-to-CSR; "
-                                  "each step = one pass over a bounded sample of the HASNEG elements on the host cores"},
+           "config": {"workload": workload_name(args.nx, R.ne, len(R.active)), "ne": R.ne, "hasneg_elements": int(len(R.active)),
+                      "nnz": int(len(R.colidx)), "colors": int(len(R.cptr) - 1), "sample_stride": stride,
+                      "note": "oracle tier T1 (SURVEY 8c): the reference's cut rule, FE and AddABt without its CoefficientFunction tree, virtual "
+                              "integrator calls and TaskManager -- faster than the real ngsxfem Assemble"},
            "cpu_baseline": info,
            "e2e": {"value": info["value"], "unit": "elements/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
     print(json.dumps(out), flush=True)

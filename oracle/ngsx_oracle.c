@@ -1178,3 +1178,94 @@ void orc_set_threads(int n)
   (void)n;
 #endif
 }
+
+/* ------------------------------------------------------------------ set-up helpers of the CPU arm (bench.py --impl reference)
+ * The reference arm must run on a GPU-less host without the product library: sparsity pattern and element colouring are
+ * built here.  Both follow NGSolve's constructions in spirit (MatrixGraph from the element -> dof table,
+ * NGS/linalg/sparsematrix.cpp; greedy element colouring, NGS/comp/fespace.cpp:598-705) -- any valid pattern / colouring
+ * gives the same CSR values up to summation order. */
+
+/* pattern of the listed elements' couplings: rowptr[ndof+1]; colidx == NULL: count only.  table [n][nd] = dofs of list entry k */
+int64_t orc_csr_pattern(int64_t n, int nd, const int32_t *table, int64_t ndof, int64_t *rowptr, int32_t *colidx)
+{
+  /* dof -> list entries (transposed table) */
+  int64_t *cnt = (int64_t *)calloc((size_t)ndof + 1, sizeof(int64_t));
+  for (int64_t p = 0; p < n*nd; p++) cnt[table[p] + 1]++;
+  for (int64_t d = 0; d < ndof; d++) cnt[d + 1] += cnt[d];
+  int32_t *d2e = (int32_t *)malloc(sizeof(int32_t) * (size_t)(n*nd > 0 ? n*nd : 1));
+  int64_t *fill = (int64_t *)malloc(sizeof(int64_t) * (size_t)(ndof > 0 ? ndof : 1));
+  memcpy(fill, cnt, sizeof(int64_t) * (size_t)ndof);
+  for (int64_t k = 0; k < n; k++) for (int i = 0; i < nd; i++) d2e[fill[table[k*nd + i]]++] = (int32_t)k;
+  free(fill);
+  if (!colidx) {
+    rowptr[0] = 0;
+#pragma omp parallel
+    {
+      int cap = 4096;
+      int32_t *buf = (int32_t *)malloc(sizeof(int32_t) * cap);
+#pragma omp for schedule(dynamic,1024)
+      for (int64_t d = 0; d < ndof; d++) {
+        int m = (int)(cnt[d + 1] - cnt[d]) * nd;
+        if (m > cap) { cap = 2*m; buf = (int32_t *)realloc(buf, sizeof(int32_t) * cap); }
+        int t = 0;
+        for (int64_t q = cnt[d]; q < cnt[d + 1]; q++) for (int j = 0; j < nd; j++) buf[t++] = table[(int64_t)d2e[q]*nd + j];
+        for (int a = 1; a < t; a++) { int32_t v = buf[a]; int b = a; while (b > 0 && buf[b-1] > v) { buf[b] = buf[b-1]; b--; } buf[b] = v; }
+        int u = 0;
+        for (int a = 0; a < t; a++) if (a == 0 || buf[a] != buf[a-1]) u++;
+        rowptr[d + 1] = u;
+      }
+      free(buf);
+    }
+    for (int64_t d = 0; d < ndof; d++) rowptr[d + 1] += rowptr[d];
+  } else {
+#pragma omp parallel
+    {
+      int cap = 4096;
+      int32_t *buf = (int32_t *)malloc(sizeof(int32_t) * cap);
+#pragma omp for schedule(dynamic,1024)
+      for (int64_t d = 0; d < ndof; d++) {
+        int m = (int)(cnt[d + 1] - cnt[d]) * nd;
+        if (m > cap) { cap = 2*m; buf = (int32_t *)realloc(buf, sizeof(int32_t) * cap); }
+        int t = 0;
+        for (int64_t q = cnt[d]; q < cnt[d + 1]; q++) for (int j = 0; j < nd; j++) buf[t++] = table[(int64_t)d2e[q]*nd + j];
+        for (int a = 1; a < t; a++) { int32_t v = buf[a]; int b = a; while (b > 0 && buf[b-1] > v) { buf[b] = buf[b-1]; b--; } buf[b] = v; }
+        int64_t o = rowptr[d];
+        for (int a = 0; a < t; a++) if (a == 0 || buf[a] != buf[a-1]) colidx[o++] = buf[a];
+      }
+      free(buf);
+    }
+  }
+  int64_t nnz = rowptr[ndof];
+  free(cnt); free(d2e);
+  return nnz;
+}
+
+/* greedy colouring of list entries: two entries of one colour share no dof.  perm[n] = colour-sorted positions,
+ * color_ptr[ncolors+1]; returns ncolors (<= 128) or -1 */
+int orc_color_elements(int64_t n, int nd, const int32_t *table, int64_t ndof, int64_t *perm, int64_t *color_ptr)
+{
+  uint64_t *used = (uint64_t *)calloc((size_t)ndof * 2 + 2, sizeof(uint64_t));
+  uint8_t *col = (uint8_t *)malloc((size_t)(n > 0 ? n : 1));
+  int ncol = 0;
+  for (int64_t k = 0; k < n; k++) {
+    uint64_t m0 = 0, m1 = 0;
+    for (int i = 0; i < nd; i++) { m0 |= used[2*(int64_t)table[k*nd + i]]; m1 |= used[2*(int64_t)table[k*nd + i] + 1]; }
+    int c;
+    if (~m0) c = __builtin_ctzll(~m0);
+    else if (~m1) c = 64 + __builtin_ctzll(~m1);
+    else { free(used); free(col); return -1; }
+    col[k] = (uint8_t)c;
+    if (c + 1 > ncol) ncol = c + 1;
+    for (int i = 0; i < nd; i++) {
+      if (c < 64) used[2*(int64_t)table[k*nd + i]] |= 1ULL << c; else used[2*(int64_t)table[k*nd + i] + 1] |= 1ULL << (c - 64);
+    }
+  }
+  for (int c = 0; c <= ncol; c++) color_ptr[c] = 0;
+  for (int64_t k = 0; k < n; k++) color_ptr[col[k] + 1]++;
+  for (int c = 0; c < ncol; c++) color_ptr[c + 1] += color_ptr[c];
+  int64_t *fill = (int64_t *)malloc(sizeof(int64_t) * (size_t)(ncol + 1));
+  memcpy(fill, color_ptr, sizeof(int64_t) * (size_t)(ncol + 1));
+  for (int64_t k = 0; k < n; k++) perm[fill[col[k]]++] = k;
+  free(fill); free(used); free(col);
+  return ncol;
+}

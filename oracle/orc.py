@@ -76,6 +76,9 @@ def load():
     L.orc_elmat_mesh_iso.restype = c_i64
     L.orc_quad_rule_untrafo.argtypes = [dp, c_int, c_int, dp, dp, c_int]
     L.orc_set_threads.argtypes = [c_int]
+    L.orc_csr_pattern.argtypes = [c_i64, c_int, ip, c_i64, lp, ip]
+    L.orc_csr_pattern.restype = c_i64
+    L.orc_color_elements.argtypes = [c_i64, c_int, ip, c_i64, lp, lp]
     _LIB = L
     return L
 

@@ -1,887 +1,3 @@
-// GENERATED by tools/gen_rule_tables.py from the compiled reference -- do not edit.
-// Reference quadrature rules of NGSolve SelectIntegrationRule (NGS/fem/intrule.cpp:2620-2659).
-// Layout per rule: npts x {xi0, xi1, xi2, weight}.  NGSX_RULE_<ET>_OFFS[order] .. [order+1] index points.
-#pragma once
-#define NGSX_RULE_SEGM_MAXORDER 16
-#define NGSX_RULE_SEGM_NPTS 81
-static const int NGSX_RULE_SEGM_OFFS[18] = {0, 1, 2, 4, 6, 9, 12, 16, 20, 25, 30, 36, 42, 49, 56, 64, 72, 81};
-static const double NGSX_RULE_SEGM_DATA[81][4] = {
-  {0.5, 0, 0, 1},
-  {0.5, 0, 0, 1},
-  {0.21132486540518713, 0, 0, 0.50000000000000011},
-  {0.78867513459481287, 0, 0, 0.50000000000000011},
-  {0.21132486540518713, 0, 0, 0.50000000000000011},
-  {0.78867513459481287, 0, 0, 0.50000000000000011},
-  {0.1127016653792583, 0, 0, 0.27777777777777635},
-  {0.5, 0, 0, 0.44444444444444442},
-  {0.8872983346207417, 0, 0, 0.27777777777777635},
-  {0.1127016653792583, 0, 0, 0.27777777777777635},
-  {0.5, 0, 0, 0.44444444444444442},
-  {0.8872983346207417, 0, 0, 0.27777777777777635},
-  {0.069431844202973714, 0, 0, 0.17392742256872379},
-  {0.33000947820757187, 0, 0, 0.32607257743127321},
-  {0.66999052179242813, 0, 0, 0.32607257743127321},
-  {0.93056815579702623, 0, 0, 0.17392742256872379},
-  {0.069431844202973714, 0, 0, 0.17392742256872379},
-  {0.33000947820757187, 0, 0, 0.32607257743127321},
-  {0.66999052179242813, 0, 0, 0.32607257743127321},
-  {0.93056815579702623, 0, 0, 0.17392742256872379},
-  {0.046910077030668018, 0, 0, 0.11846344252809086},
-  {0.23076534494715845, 0, 0, 0.23931433524968324},
-  {0.5, 0, 0, 0.28444444444444444},
-  {0.7692346550528415, 0, 0, 0.23931433524968324},
-  {0.95308992296933193, 0, 0, 0.11846344252809086},
-  {0.046910077030668018, 0, 0, 0.11846344252809086},
-  {0.23076534494715845, 0, 0, 0.23931433524968324},
-  {0.5, 0, 0, 0.28444444444444444},
-  {0.7692346550528415, 0, 0, 0.23931433524968324},
-  {0.95308992296933193, 0, 0, 0.11846344252809086},
-  {0.033765242898423975, 0, 0, 0.085662246189581168},
-  {0.1693953067668677, 0, 0, 0.1803807865240693},
-  {0.38069040695840156, 0, 0, 0.23395696728634474},
-  {0.61930959304159849, 0, 0, 0.23395696728634474},
-  {0.83060469323313235, 0, 0, 0.1803807865240693},
-  {0.96623475710157603, 0, 0, 0.085662246189581168},
-  {0.033765242898423975, 0, 0, 0.085662246189581168},
-  {0.1693953067668677, 0, 0, 0.1803807865240693},
-  {0.38069040695840156, 0, 0, 0.23395696728634474},
-  {0.61930959304159849, 0, 0, 0.23395696728634474},
-  {0.83060469323313235, 0, 0, 0.1803807865240693},
-  {0.96623475710157603, 0, 0, 0.085662246189581168},
-  {0.025446043828620757, 0, 0, 0.064742483084431229},
-  {0.12923440720030277, 0, 0, 0.13985269574463835},
-  {0.29707742431130141, 0, 0, 0.19091502525255952},
-  {0.5, 0, 0, 0.2089795918367347},
-  {0.70292257568869854, 0, 0, 0.19091502525255952},
-  {0.87076559279969723, 0, 0, 0.13985269574463835},
-  {0.97455395617137919, 0, 0, 0.064742483084431229},
-  {0.025446043828620757, 0, 0, 0.064742483084431229},
-  {0.12923440720030277, 0, 0, 0.13985269574463835},
-  {0.29707742431130141, 0, 0, 0.19091502525255952},
-  {0.5, 0, 0, 0.2089795918367347},
-  {0.70292257568869854, 0, 0, 0.19091502525255952},
-  {0.87076559279969723, 0, 0, 0.13985269574463835},
-  {0.97455395617137919, 0, 0, 0.064742483084431229},
-  {0.019855071751231912, 0, 0, 0.050614268145184861},
-  {0.10166676129318658, 0, 0, 0.11119051722668723},
-  {0.2372337950418355, 0, 0, 0.15685332293894369},
-  {0.40828267875217511, 0, 0, 0.181341891689181},
-  {0.59171732124782483, 0, 0, 0.181341891689181},
-  {0.7627662049581645, 0, 0, 0.15685332293894369},
-  {0.89833323870681348, 0, 0, 0.11119051722668723},
-  {0.98014492824876809, 0, 0, 0.050614268145184861},
-  {0.019855071751231912, 0, 0, 0.050614268145184861},
-  {0.10166676129318658, 0, 0, 0.11119051722668723},
-  {0.2372337950418355, 0, 0, 0.15685332293894369},
-  {0.40828267875217511, 0, 0, 0.181341891689181},
-  {0.59171732124782483, 0, 0, 0.181341891689181},
-  {0.7627662049581645, 0, 0, 0.15685332293894369},
-  {0.89833323870681348, 0, 0, 0.11119051722668723},
-  {0.98014492824876809, 0, 0, 0.050614268145184861},
-  {0.015919880246186957, 0, 0, 0.040637194180784368},
-  {0.08198444633668206, 0, 0, 0.090324080347428781},
-  {0.19331428364970477, 0, 0, 0.13030534820146777},
-  {0.33787328829809549, 0, 0, 0.15617353852000107},
-  {0.5, 0, 0, 0.16511967750062989},
-  {0.66212671170190451, 0, 0, 0.15617353852000107},
-  {0.80668571635029518, 0, 0, 0.13030534820146777},
-  {0.91801555366331788, 0, 0, 0.090324080347428781},
-  {0.98408011975381304, 0, 0, 0.040637194180784368},
-};
-#define NGSX_RULE_TRIG_MAXORDER 16
-#define NGSX_RULE_TRIG_NPTS 486
-static const int NGSX_RULE_TRIG_OFFS[18] = {0, 1, 2, 5, 11, 17, 29, 41, 57, 82, 107, 143, 179, 228, 277, 341, 405, 486};
-static const double NGSX_RULE_TRIG_DATA[486][4] = {
-  {0.33333333333333331, 0.33333333333333331, 0, 0.5},
-  {0.33333333333333331, 0.33333333333333331, 0, 0.5},
-  {0, 0.5, 0, 0.16666666666666666},
-  {0.5, 0, 0, 0.16666666666666666},
-  {0.5, 0.5, 0, 0.16666666666666666},
-  {0.81684757298045896, 0.091576213509771007, 0, 0.054975871827660998},
-  {0.091576213509771007, 0.81684757298045896, 0, 0.054975871827660998},
-  {0.091576213509771007, 0.091576213509771007, 0, 0.054975871827660998},
-  {0.10810301816807, 0.445948490915965, 0, 0.111690794839005},
-  {0.445948490915965, 0.10810301816807, 0, 0.111690794839005},
-  {0.445948490915965, 0.445948490915965, 0, 0.111690794839005},
-  {0.81684757298045896, 0.091576213509771007, 0, 0.054975871827660998},
-  {0.091576213509771007, 0.81684757298045896, 0, 0.054975871827660998},
-  {0.091576213509771007, 0.091576213509771007, 0, 0.054975871827660998},
-  {0.10810301816807, 0.445948490915965, 0, 0.111690794839005},
-  {0.445948490915965, 0.10810301816807, 0, 0.111690794839005},
-  {0.445948490915965, 0.445948490915965, 0, 0.111690794839005},
-  {0.87382197101699599, 0.063089014491502005, 0, 0.025422453185103},
-  {0.063089014491502005, 0.87382197101699599, 0, 0.025422453185103},
-  {0.063089014491502005, 0.063089014491502005, 0, 0.025422453185103},
-  {0.50142650965817903, 0.24928674517091001, 0, 0.058393137863188997},
-  {0.24928674517091001, 0.50142650965817903, 0, 0.058393137863188997},
-  {0.24928674517091001, 0.24928674517091001, 0, 0.058393137863188997},
-  {0.636502499121399, 0.310352451033785, 0, 0.041425537809187001},
-  {0.310352451033785, 0.053145049844816002, 0, 0.041425537809187001},
-  {0.053145049844816002, 0.636502499121399, 0, 0.041425537809187001},
-  {0.636502499121399, 0.053145049844816002, 0, 0.041425537809187001},
-  {0.310352451033785, 0.636502499121399, 0, 0.041425537809187001},
-  {0.053145049844816002, 0.310352451033785, 0, 0.041425537809187001},
-  {0.87382197101699599, 0.063089014491502005, 0, 0.025422453185103},
-  {0.063089014491502005, 0.87382197101699599, 0, 0.025422453185103},
-  {0.063089014491502005, 0.063089014491502005, 0, 0.025422453185103},
-  {0.50142650965817903, 0.24928674517091001, 0, 0.058393137863188997},
-  {0.24928674517091001, 0.50142650965817903, 0, 0.058393137863188997},
-  {0.24928674517091001, 0.24928674517091001, 0, 0.058393137863188997},
-  {0.636502499121399, 0.310352451033785, 0, 0.041425537809187001},
-  {0.310352451033785, 0.053145049844816002, 0, 0.041425537809187001},
-  {0.053145049844816002, 0.636502499121399, 0, 0.041425537809187001},
-  {0.636502499121399, 0.053145049844816002, 0, 0.041425537809187001},
-  {0.310352451033785, 0.636502499121399, 0, 0.041425537809187001},
-  {0.053145049844816002, 0.310352451033785, 0, 0.041425537809187001},
-  {0.86024013565621948, 0.0097037851269461094, 0, 0.0054232259105251581},
-  {0.58359043236891683, 0.028912084224389012, 0, 0.022584049282368273},
-  {0.2768430136381238, 0.050210123211369778, 0, 0.035388067898085011},
-  {0.057104196114517725, 0.065466994555014452, 0, 0.023568368193381869},
-  {0.86024013565621948, 0.046122079906452035, 0, 0.010167259564478793},
-  {0.58359043236891683, 0.13741910413457437, 0, 0.042339724521743963},
-  {0.2768430136381238, 0.23864865973144292, 0, 0.0663442161070492},
-  {0.057104196114517725, 0.31116455224435702, 0, 0.044185088522361679},
-  {0.86024013565621948, 0.093637784437328481, 0, 0.010167259564478793},
-  {0.58359043236891683, 0.2789904634965088, 0, 0.042339724521743963},
-  {0.2768430136381238, 0.48450832663043325, 0, 0.0663442161070492},
-  {0.057104196114517725, 0.6317312516411252, 0, 0.044185088522361679},
-  {0.86024013565621948, 0.1300560792168344, 0, 0.0054232259105251581},
-  {0.58359043236891683, 0.38749748340669415, 0, 0.022584049282368273},
-  {0.2768430136381238, 0.67294686315050634, 0, 0.035388067898085011},
-  {0.057104196114517725, 0.87742880933046774, 0, 0.023568368193381869},
-  {0.90146491420117358, 0.0046222884650464298, 0, 0.0018655521668774371},
-  {0.69546427335363603, 0.014285794395571393, 0, 0.0087554991821635619},
-  {0.43797481024738616, 0.026364644944470925, 0, 0.017341506431365162},
-  {0.19801341787360816, 0.037621252345111204, 0, 0.019804083132046735},
-  {0.039809857051468778, 0.045042593569803738, 0, 0.011465080351592211},
-  {0.90146491420117358, 0.022738483063764033, 0, 0.0037687016953269264},
-  {0.69546427335363603, 0.070276292008281727, 0, 0.017687452110483469},
-  {0.43797481024738616, 0.12969593678225411, 0, 0.035032504503371718},
-  {0.19801341787360816, 0.18507071026738944, 0, 0.040007287386160419},
-  {0.039809857051468778, 0.22157860955237918, 0, 0.023161221929498425},
-  {0.90146491420117358, 0.049267542899413208, 0, 0.0044794067972805341},
-  {0.69546427335363603, 0.15226786332318198, 0, 0.021022967487322079},
-  {0.43797481024738616, 0.28101259487630692, 0, 0.041638965215194966},
-  {0.19801341787360816, 0.40099329106319592, 0, 0.047551897057953998},
-  {0.039809857051468778, 0.48009507147426561, 0, 0.027528985664469856},
-  {0.90146491420117358, 0.075796602735062377, 0, 0.0037687016953269264},
-  {0.69546427335363603, 0.23425943463808221, 0, 0.017687452110483469},
-  {0.43797481024738616, 0.43232925297035968, 0, 0.035032504503371718},
-  {0.19801341787360816, 0.61691587185900232, 0, 0.040007287386160419},
-  {0.039809857051468778, 0.73861153339615193, 0, 0.023161221929498425},
-  {0.90146491420117358, 0.093912797333779982, 0, 0.0018655521668774371},
-  {0.69546427335363603, 0.29024993225079254, 0, 0.0087554991821635619},
-  {0.43797481024738616, 0.53566054480814285, 0, 0.017341506431365162},
-  {0.19801341787360816, 0.76436532978128058, 0, 0.019804083132046735},
-  {0.039809857051468778, 0.91514754937872744, 0, 0.011465080351592211},
-  {0.90146491420117358, 0.0046222884650464298, 0, 0.0018655521668774371},
-  {0.69546427335363603, 0.014285794395571393, 0, 0.0087554991821635619},
-  {0.43797481024738616, 0.026364644944470925, 0, 0.017341506431365162},
-  {0.19801341787360816, 0.037621252345111204, 0, 0.019804083132046735},
-  {0.039809857051468778, 0.045042593569803738, 0, 0.011465080351592211},
-  {0.90146491420117358, 0.022738483063764033, 0, 0.0037687016953269264},
-  {0.69546427335363603, 0.070276292008281727, 0, 0.017687452110483469},
-  {0.43797481024738616, 0.12969593678225411, 0, 0.035032504503371718},
-  {0.19801341787360816, 0.18507071026738944, 0, 0.040007287386160419},
-  {0.039809857051468778, 0.22157860955237918, 0, 0.023161221929498425},
-  {0.90146491420117358, 0.049267542899413208, 0, 0.0044794067972805341},
-  {0.69546427335363603, 0.15226786332318198, 0, 0.021022967487322079},
-  {0.43797481024738616, 0.28101259487630692, 0, 0.041638965215194966},
-  {0.19801341787360816, 0.40099329106319592, 0, 0.047551897057953998},
-  {0.039809857051468778, 0.48009507147426561, 0, 0.027528985664469856},
-  {0.90146491420117358, 0.075796602735062377, 0, 0.0037687016953269264},
-  {0.69546427335363603, 0.23425943463808221, 0, 0.017687452110483469},
-  {0.43797481024738616, 0.43232925297035968, 0, 0.035032504503371718},
-  {0.19801341787360816, 0.61691587185900232, 0, 0.040007287386160419},
-  {0.039809857051468778, 0.73861153339615193, 0, 0.023161221929498425},
-  {0.90146491420117358, 0.093912797333779982, 0, 0.0018655521668774371},
-  {0.69546427335363603, 0.29024993225079254, 0, 0.0087554991821635619},
-  {0.43797481024738616, 0.53566054480814285, 0, 0.017341506431365162},
-  {0.19801341787360816, 0.76436532978128058, 0, 0.019804083132046735},
-  {0.039809857051468778, 0.91514754937872744, 0, 0.011465080351592211},
-  {0.92694567131974115, 0.0024666971526702409, 0, 0.00074854256123628199},
-  {0.7692338620300545, 0.007791874701286429, 0, 0.0037652982126914975},
-  {0.55867151877155008, 0.014901563366671157, 0, 0.0084515357969427267},
-  {0.3369846902811543, 0.022386872978030627, 0, 0.012060606404264545},
-  {0.1480785996684843, 0.028765333012559118, 0, 0.011610874766996971},
-  {0.029316427159784886, 0.032775366614459886, 0, 0.0061942653526585421},
-  {0.92694567131974115, 0.012375060417440029, 0, 0.0015762217540235858},
-  {0.7692338620300545, 0.039090700732824231, 0, 0.0079286673337964873},
-  {0.55867151877155008, 0.074758973462649092, 0, 0.017796575997026279},
-  {0.3369846902811543, 0.11231168178095367, 0, 0.025396271589047656},
-  {0.1480785996684843, 0.1443114869504166, 0, 0.024449262258057814},
-  {0.029316427159784886, 0.16442924159482741, 0, 0.013043394330082793},
-  {0.92694567131974115, 0.027811082115360569, 0, 0.0020443865915448487},
-  {0.7692338620300545, 0.087850454975997194, 0, 0.010283617228766299},
-  {0.55867151877155008, 0.16800951912119189, 0, 0.023082463651358156},
-  {0.3369846902811543, 0.25240356807651804, 0, 0.032939398900786593},
-  {0.1480785996684843, 0.32431830458877603, 0, 0.031711111590703868},
-  {0.029316427159784886, 0.36952992437237669, 0, 0.016917505680012556},
-  {0.92694567131974115, 0.045243246564898289, 0, 0.0020443865915448487},
-  {0.7692338620300545, 0.1429156829939483, 0, 0.010283617228766299},
-  {0.55867151877155008, 0.27331896210725803, 0, 0.023082463651358156},
-  {0.3369846902811543, 0.41061174164232772, 0, 0.032939398900786593},
-  {0.1480785996684843, 0.52760309574273967, 0, 0.031711111590703868},
-  {0.029316427159784886, 0.60115364846783848, 0, 0.016917505680012556},
-  {0.92694567131974115, 0.060679268262818824, 0, 0.0015762217540235858},
-  {0.7692338620300545, 0.19167543723712127, 0, 0.0079286673337964873},
-  {0.55867151877155008, 0.36656950776580083, 0, 0.017796575997026279},
-  {0.3369846902811543, 0.55070362793789207, 0, 0.025396271589047656},
-  {0.1480785996684843, 0.70760991338109913, 0, 0.024449262258057814},
-  {0.029316427159784886, 0.80625433124538781, 0, 0.013043394330082793},
-  {0.92694567131974115, 0.07058763152758861, 0, 0.00074854256123628199},
-  {0.7692338620300545, 0.22297426326865907, 0, 0.0037652982126914975},
-  {0.55867151877155008, 0.42642691786177878, 0, 0.0084515357969427267},
-  {0.3369846902811543, 0.64062843674081504, 0, 0.012060606404264545},
-  {0.1480785996684843, 0.82315606731895652, 0, 0.011610874766996971},
-  {0.029316427159784886, 0.93790820622575521, 0, 0.0061942653526585421},
-  {0.92694567131974115, 0.0024666971526702409, 0, 0.00074854256123628199},
-  {0.7692338620300545, 0.007791874701286429, 0, 0.0037652982126914975},
-  {0.55867151877155008, 0.014901563366671157, 0, 0.0084515357969427267},
-  {0.3369846902811543, 0.022386872978030627, 0, 0.012060606404264545},
-  {0.1480785996684843, 0.028765333012559118, 0, 0.011610874766996971},
-  {0.029316427159784886, 0.032775366614459886, 0, 0.0061942653526585421},
-  {0.92694567131974115, 0.012375060417440029, 0, 0.0015762217540235858},
-  {0.7692338620300545, 0.039090700732824231, 0, 0.0079286673337964873},
-  {0.55867151877155008, 0.074758973462649092, 0, 0.017796575997026279},
-  {0.3369846902811543, 0.11231168178095367, 0, 0.025396271589047656},
-  {0.1480785996684843, 0.1443114869504166, 0, 0.024449262258057814},
-  {0.029316427159784886, 0.16442924159482741, 0, 0.013043394330082793},
-  {0.92694567131974115, 0.027811082115360569, 0, 0.0020443865915448487},
-  {0.7692338620300545, 0.087850454975997194, 0, 0.010283617228766299},
-  {0.55867151877155008, 0.16800951912119189, 0, 0.023082463651358156},
-  {0.3369846902811543, 0.25240356807651804, 0, 0.032939398900786593},
-  {0.1480785996684843, 0.32431830458877603, 0, 0.031711111590703868},
-  {0.029316427159784886, 0.36952992437237669, 0, 0.016917505680012556},
-  {0.92694567131974115, 0.045243246564898289, 0, 0.0020443865915448487},
-  {0.7692338620300545, 0.1429156829939483, 0, 0.010283617228766299},
-  {0.55867151877155008, 0.27331896210725803, 0, 0.023082463651358156},
-  {0.3369846902811543, 0.41061174164232772, 0, 0.032939398900786593},
-  {0.1480785996684843, 0.52760309574273967, 0, 0.031711111590703868},
-  {0.029316427159784886, 0.60115364846783848, 0, 0.016917505680012556},
-  {0.92694567131974115, 0.060679268262818824, 0, 0.0015762217540235858},
-  {0.7692338620300545, 0.19167543723712127, 0, 0.0079286673337964873},
-  {0.55867151877155008, 0.36656950776580083, 0, 0.017796575997026279},
-  {0.3369846902811543, 0.55070362793789207, 0, 0.025396271589047656},
-  {0.1480785996684843, 0.70760991338109913, 0, 0.024449262258057814},
-  {0.029316427159784886, 0.80625433124538781, 0, 0.013043394330082793},
-  {0.92694567131974115, 0.07058763152758861, 0, 0.00074854256123628199},
-  {0.7692338620300545, 0.22297426326865907, 0, 0.0037652982126914975},
-  {0.55867151877155008, 0.42642691786177878, 0, 0.0084515357969427267},
-  {0.3369846902811543, 0.64062843674081504, 0, 0.012060606404264545},
-  {0.1480785996684843, 0.82315606731895652, 0, 0.011610874766996971},
-  {0.029316427159784886, 0.93790820622575521, 0, 0.0061942653526585421},
-  {0.94373743946307787, 0.0014316595813329493, 0, 0.0003375907567113562},
-  {0.81975930826310761, 0.0045864125416378871, 0, 0.0017744850714379531},
-  {0.64737528288683033, 0.0089729040067167108, 0, 0.0042979100879821808},
-  {0.45284637366944464, 0.013922895156596097, 0, 0.0069355427537336842},
-  {0.26578982278458946, 0.018682744348842751, 0, 0.0082476030135291145},
-  {0.11467905316090421, 0.022527915615663658, 0, 0.0071546437790957415},
-  {0.022479386438712501, 0.024874032376060777, 0, 0.0036234660797252538},
-  {0.94373743946307787, 0.0072710586585602805, 0, 0.0007292426106515667},
-  {0.81975930826310761, 0.023293298949989799, 0, 0.0038331325734846898},
-  {0.64737528288683033, 0.045571246280294943, 0, 0.0092840787568885443},
-  {0.45284637366944464, 0.070711074546325303, 0, 0.014981729219389414},
-  {0.26578982278458946, 0.09488521701286283, 0, 0.017815960400675797},
-  {0.11467905316090421, 0.1144139277467613, 0, 0.01545501766273407},
-  {0.022479386438712501, 0.12632929701966925, 0, 0.0078271866484943831},
-  {0.94373743946307787, 0.016714336569467501, 0, 0.0009955000916249681},
-  {0.81975930826310761, 0.05354544045728326, 0, 0.0052326671156876416},
-  {0.64737528288683033, 0.10475684270848173, 0, 0.012673836002092797},
-  {0.45284637366944464, 0.16254699001286968, 0, 0.020451784622509815},
-  {0.26578982278458946, 0.21811726835029835, 0, 0.024320836374897122},
-  {0.11467905316090421, 0.26300886657580119, 0, 0.021097877818152446},
-  {0.022479386438712501, 0.29039930608799031, 0, 0.010685010601313997},
-  {0.94373743946307787, 0.028131280268461067, 0, 0.001089695284831589},
-  {0.81975930826310761, 0.090120345868446194, 0, 0.0057277872006527512},
-  {0.64737528288683033, 0.17631235855658484, 0, 0.013873046771563926},
-  {0.45284637366944464, 0.27357681316527771, 0, 0.022386952504607066},
-  {0.26578982278458946, 0.3671050886077053, 0, 0.026622097721383357},
-  {0.11467905316090421, 0.4426604734195479, 0, 0.023094179670909303},
-  {0.022479386438712501, 0.48876030678064375, 0, 0.011696036764418287},
-  {0.94373743946307787, 0.039548223967454631, 0, 0.0009955000916249681},
-  {0.81975930826310761, 0.12669525127960912, 0, 0.0052326671156876416},
-  {0.64737528288683033, 0.24786787440468791, 0, 0.012673836002092797},
-  {0.45284637366944464, 0.38460663631768571, 0, 0.020451784622509815},
-  {0.26578982278458946, 0.51609290886511228, 0, 0.024320836374897122},
-  {0.11467905316090421, 0.62231208026329454, 0, 0.021097877818152446},
-  {0.022479386438712501, 0.68712130747329714, 0, 0.010685010601313997},
-  {0.94373743946307787, 0.048991501878361855, 0, 0.0007292426106515667},
-  {0.81975930826310761, 0.15694739278690259, 0, 0.0038331325734846898},
-  {0.64737528288683033, 0.30705347083287471, 0, 0.0092840787568885443},
-  {0.45284637366944464, 0.47644255178423012, 0, 0.014981729219389414},
-  {0.26578982278458946, 0.63932496020254781, 0, 0.017815960400675797},
-  {0.11467905316090421, 0.7709070190923345, 0, 0.01545501766273407},
-  {0.022479386438712501, 0.85119131654161828, 0, 0.0078271866484943831},
-  {0.94373743946307787, 0.054830900955589179, 0, 0.0003375907567113562},
-  {0.81975930826310761, 0.1756542791952545, 0, 0.0017744850714379531},
-  {0.64737528288683033, 0.34365181310645293, 0, 0.0042979100879821808},
-  {0.45284637366944464, 0.53323073117395925, 0, 0.0069355427537336842},
-  {0.26578982278458946, 0.71552743286656784, 0, 0.0082476030135291145},
-  {0.11467905316090421, 0.86279303122343209, 0, 0.0071546437790957415},
-  {0.022479386438712501, 0.95264658118522672, 0, 0.0036234660797252538},
-  {0.94373743946307787, 0.0014316595813329493, 0, 0.0003375907567113562},
-  {0.81975930826310761, 0.0045864125416378871, 0, 0.0017744850714379531},
-  {0.64737528288683033, 0.0089729040067167108, 0, 0.0042979100879821808},
-  {0.45284637366944464, 0.013922895156596097, 0, 0.0069355427537336842},
-  {0.26578982278458946, 0.018682744348842751, 0, 0.0082476030135291145},
-  {0.11467905316090421, 0.022527915615663658, 0, 0.0071546437790957415},
-  {0.022479386438712501, 0.024874032376060777, 0, 0.0036234660797252538},
-  {0.94373743946307787, 0.0072710586585602805, 0, 0.0007292426106515667},
-  {0.81975930826310761, 0.023293298949989799, 0, 0.0038331325734846898},
-  {0.64737528288683033, 0.045571246280294943, 0, 0.0092840787568885443},
-  {0.45284637366944464, 0.070711074546325303, 0, 0.014981729219389414},
-  {0.26578982278458946, 0.09488521701286283, 0, 0.017815960400675797},
-  {0.11467905316090421, 0.1144139277467613, 0, 0.01545501766273407},
-  {0.022479386438712501, 0.12632929701966925, 0, 0.0078271866484943831},
-  {0.94373743946307787, 0.016714336569467501, 0, 0.0009955000916249681},
-  {0.81975930826310761, 0.05354544045728326, 0, 0.0052326671156876416},
-  {0.64737528288683033, 0.10475684270848173, 0, 0.012673836002092797},
-  {0.45284637366944464, 0.16254699001286968, 0, 0.020451784622509815},
-  {0.26578982278458946, 0.21811726835029835, 0, 0.024320836374897122},
-  {0.11467905316090421, 0.26300886657580119, 0, 0.021097877818152446},
-  {0.022479386438712501, 0.29039930608799031, 0, 0.010685010601313997},
-  {0.94373743946307787, 0.028131280268461067, 0, 0.001089695284831589},
-  {0.81975930826310761, 0.090120345868446194, 0, 0.0057277872006527512},
-  {0.64737528288683033, 0.17631235855658484, 0, 0.013873046771563926},
-  {0.45284637366944464, 0.27357681316527771, 0, 0.022386952504607066},
-  {0.26578982278458946, 0.3671050886077053, 0, 0.026622097721383357},
-  {0.11467905316090421, 0.4426604734195479, 0, 0.023094179670909303},
-  {0.022479386438712501, 0.48876030678064375, 0, 0.011696036764418287},
-  {0.94373743946307787, 0.039548223967454631, 0, 0.0009955000916249681},
-  {0.81975930826310761, 0.12669525127960912, 0, 0.0052326671156876416},
-  {0.64737528288683033, 0.24786787440468791, 0, 0.012673836002092797},
-  {0.45284637366944464, 0.38460663631768571, 0, 0.020451784622509815},
-  {0.26578982278458946, 0.51609290886511228, 0, 0.024320836374897122},
-  {0.11467905316090421, 0.62231208026329454, 0, 0.021097877818152446},
-  {0.022479386438712501, 0.68712130747329714, 0, 0.010685010601313997},
-  {0.94373743946307787, 0.048991501878361855, 0, 0.0007292426106515667},
-  {0.81975930826310761, 0.15694739278690259, 0, 0.0038331325734846898},
-  {0.64737528288683033, 0.30705347083287471, 0, 0.0092840787568885443},
-  {0.45284637366944464, 0.47644255178423012, 0, 0.014981729219389414},
-  {0.26578982278458946, 0.63932496020254781, 0, 0.017815960400675797},
-  {0.11467905316090421, 0.7709070190923345, 0, 0.01545501766273407},
-  {0.022479386438712501, 0.85119131654161828, 0, 0.0078271866484943831},
-  {0.94373743946307787, 0.054830900955589179, 0, 0.0003375907567113562},
-  {0.81975930826310761, 0.1756542791952545, 0, 0.0017744850714379531},
-  {0.64737528288683033, 0.34365181310645293, 0, 0.0042979100879821808},
-  {0.45284637366944464, 0.53323073117395925, 0, 0.0069355427537336842},
-  {0.26578982278458946, 0.71552743286656784, 0, 0.0082476030135291145},
-  {0.11467905316090421, 0.86279303122343209, 0, 0.0071546437790957415},
-  {0.022479386438712501, 0.95264658118522672, 0, 0.0036234660797252538},
-  {0.95536604471003006, 0.00088621038482363033, 0, 0.00016678370324769984},
-  {0.85563374295785444, 0.0028664023920285894, 0, 0.0009031054595185176},
-  {0.71317524285556955, 0.0056949261331323345, 0, 0.0022998779017455581},
-  {0.54518668480342669, 0.0090303510066436186, 0, 0.0040086297656954876},
-  {0.37193216458327227, 0.012470331936840044, 0, 0.0053675094865790664},
-  {0.21430847939563075, 0.01559996151593426, 0, 0.0056943987023078914},
-  {0.09132360789979399, 0.018041834963800133, 0, 0.004611922695458035},
-  {0.01777991514736349, 0.019502050260250196, 0, 0.0022549063580394471},
-  {0.95536604471003006, 0.0045377896780361363, 0, 0.00036639404082459889},
-  {0.85563374295785444, 0.014677249793494629, 0, 0.001983961575144539},
-  {0.71317524285556955, 0.029160544117579023, 0, 0.0050524214381561664},
-  {0.54518668480342669, 0.04623939674905285, 0, 0.0088062444316974395},
-  {0.37193216458327227, 0.063853622699240858, 0, 0.011791460746205698},
-  {0.21430847939563075, 0.079878712275365193, 0, 0.012509578034169922},
-  {0.09132360789979399, 0.092382185848405657, 0, 0.010131571367317327},
-  {0.01777991514736349, 0.099859134904086475, 0, 0.0049536269798263225},
-  {0.95536604471003006, 0.010588682601167179, 0, 0.00051686172743669657},
-  {0.85563374295785444, 0.034248555034093305, 0, 0.0027987185724675425},
-  {0.71317524285556955, 0.06804452564932606, 0, 0.0071273082563963778},
-  {0.54518668480342669, 0.10789708879964161, 0, 0.012422720355803735},
-  {0.37193216458327227, 0.14899891613962127, 0, 0.016633880716426491},
-  {0.21430847939563075, 0.18639258116516502, 0, 0.017646908496911137},
-  {0.09132360789979399, 0.21556874896285483, 0, 0.014292321640314826},
-  {0.01777991514736349, 0.23301579829590466, 0, 0.0069879417037127843},
-  {0.95536604471003006, 0.018223270829093745, 0, 0.00059755624961540024},
-  {0.85563374295785444, 0.058942242146592251, 0, 0.003235665720862453},
-  {0.71317524285556955, 0.11710558017937014, 0, 0.008240052156051194},
-  {0.54518668480342669, 0.18569239866061429, 0, 0.014362205192962652},
-  {0.37193216458327227, 0.25642921828202181, 0, 0.01923082876875444},
-  {0.21430847939563075, 0.32078423870522166, 0, 0.020402014502054377},
-  {0.09132360789979399, 0.37099683148553392, 0, 0.016523696115088263},
-  {0.01777991514736349, 0.40102344736782319, 0, 0.0080789271391991102},
-  {0.95536604471003006, 0.026410684460876195, 0, 0.00059755624961540024},
-  {0.85563374295785444, 0.085424014895553305, 0, 0.003235665720862453},
-  {0.71317524285556955, 0.16971917696506031, 0, 0.008240052156051194},
-  {0.54518668480342669, 0.26912091653595899, 0, 0.014362205192962652},
-  {0.37193216458327227, 0.37163861713470586, 0, 0.01923082876875444},
-  {0.21430847939563075, 0.4649072818991476, 0, 0.020402014502054377},
-  {0.09132360789979399, 0.53767956061467204, 0, 0.016523696115088263},
-  {0.01777991514736349, 0.58119663748481332, 0, 0.0080789271391991102},
-  {0.95536604471003006, 0.034045272688802759, 0, 0.00051686172743669657},
-  {0.85563374295785444, 0.11011770200805227, 0, 0.0027987185724675425},
-  {0.71317524285556955, 0.21878023149510439, 0, 0.0071273082563963778},
-  {0.54518668480342669, 0.3469162263969317, 0, 0.012422720355803735},
-  {0.37193216458327227, 0.47906891927710649, 0, 0.016633880716426491},
-  {0.21430847939563075, 0.59929893943920431, 0, 0.017646908496911137},
-  {0.09132360789979399, 0.69310764313735118, 0, 0.014292321640314826},
-  {0.01777991514736349, 0.74920428655673188, 0, 0.0069879417037127843},
-  {0.95536604471003006, 0.040096165611933805, 0, 0.00036639404082459889},
-  {0.85563374295785444, 0.12968900724865093, 0, 0.001983961575144539},
-  {0.71317524285556955, 0.25766421302685144, 0, 0.0050524214381561664},
-  {0.54518668480342669, 0.4085739184475205, 0, 0.0088062444316974395},
-  {0.37193216458327227, 0.56421421271748695, 0, 0.011791460746205698},
-  {0.21430847939563075, 0.70581280832900417, 0, 0.012509578034169922},
-  {0.09132360789979399, 0.81629420625180038, 0, 0.010131571367317327},
-  {0.01777991514736349, 0.88236094994855019, 0, 0.0049536269798263225},
-  {0.95536604471003006, 0.04374774490514631, 0, 0.00016678370324769984},
-  {0.85563374295785444, 0.14149985465011697, 0, 0.0009031054595185176},
-  {0.71317524285556955, 0.28112983101129813, 0, 0.0022998779017455581},
-  {0.54518668480342669, 0.44578296418992969, 0, 0.0040086297656954876},
-  {0.37193216458327227, 0.61559750347988773, 0, 0.0053675094865790664},
-  {0.21430847939563075, 0.77009155908843507, 0, 0.0056943987023078914},
-  {0.09132360789979399, 0.89063455713640582, 0, 0.004611922695458035},
-  {0.01777991514736349, 0.96271803459238636, 0, 0.0022549063580394471},
-  {0.95536604471003006, 0.00088621038482363033, 0, 0.00016678370324769984},
-  {0.85563374295785444, 0.0028664023920285894, 0, 0.0009031054595185176},
-  {0.71317524285556955, 0.0056949261331323345, 0, 0.0022998779017455581},
-  {0.54518668480342669, 0.0090303510066436186, 0, 0.0040086297656954876},
-  {0.37193216458327227, 0.012470331936840044, 0, 0.0053675094865790664},
-  {0.21430847939563075, 0.01559996151593426, 0, 0.0056943987023078914},
-  {0.09132360789979399, 0.018041834963800133, 0, 0.004611922695458035},
-  {0.01777991514736349, 0.019502050260250196, 0, 0.0022549063580394471},
-  {0.95536604471003006, 0.0045377896780361363, 0, 0.00036639404082459889},
-  {0.85563374295785444, 0.014677249793494629, 0, 0.001983961575144539},
-  {0.71317524285556955, 0.029160544117579023, 0, 0.0050524214381561664},
-  {0.54518668480342669, 0.04623939674905285, 0, 0.0088062444316974395},
-  {0.37193216458327227, 0.063853622699240858, 0, 0.011791460746205698},
-  {0.21430847939563075, 0.079878712275365193, 0, 0.012509578034169922},
-  {0.09132360789979399, 0.092382185848405657, 0, 0.010131571367317327},
-  {0.01777991514736349, 0.099859134904086475, 0, 0.0049536269798263225},
-  {0.95536604471003006, 0.010588682601167179, 0, 0.00051686172743669657},
-  {0.85563374295785444, 0.034248555034093305, 0, 0.0027987185724675425},
-  {0.71317524285556955, 0.06804452564932606, 0, 0.0071273082563963778},
-  {0.54518668480342669, 0.10789708879964161, 0, 0.012422720355803735},
-  {0.37193216458327227, 0.14899891613962127, 0, 0.016633880716426491},
-  {0.21430847939563075, 0.18639258116516502, 0, 0.017646908496911137},
-  {0.09132360789979399, 0.21556874896285483, 0, 0.014292321640314826},
-  {0.01777991514736349, 0.23301579829590466, 0, 0.0069879417037127843},
-  {0.95536604471003006, 0.018223270829093745, 0, 0.00059755624961540024},
-  {0.85563374295785444, 0.058942242146592251, 0, 0.003235665720862453},
-  {0.71317524285556955, 0.11710558017937014, 0, 0.008240052156051194},
-  {0.54518668480342669, 0.18569239866061429, 0, 0.014362205192962652},
-  {0.37193216458327227, 0.25642921828202181, 0, 0.01923082876875444},
-  {0.21430847939563075, 0.32078423870522166, 0, 0.020402014502054377},
-  {0.09132360789979399, 0.37099683148553392, 0, 0.016523696115088263},
-  {0.01777991514736349, 0.40102344736782319, 0, 0.0080789271391991102},
-  {0.95536604471003006, 0.026410684460876195, 0, 0.00059755624961540024},
-  {0.85563374295785444, 0.085424014895553305, 0, 0.003235665720862453},
-  {0.71317524285556955, 0.16971917696506031, 0, 0.008240052156051194},
-  {0.54518668480342669, 0.26912091653595899, 0, 0.014362205192962652},
-  {0.37193216458327227, 0.37163861713470586, 0, 0.01923082876875444},
-  {0.21430847939563075, 0.4649072818991476, 0, 0.020402014502054377},
-  {0.09132360789979399, 0.53767956061467204, 0, 0.016523696115088263},
-  {0.01777991514736349, 0.58119663748481332, 0, 0.0080789271391991102},
-  {0.95536604471003006, 0.034045272688802759, 0, 0.00051686172743669657},
-  {0.85563374295785444, 0.11011770200805227, 0, 0.0027987185724675425},
-  {0.71317524285556955, 0.21878023149510439, 0, 0.0071273082563963778},
-  {0.54518668480342669, 0.3469162263969317, 0, 0.012422720355803735},
-  {0.37193216458327227, 0.47906891927710649, 0, 0.016633880716426491},
-  {0.21430847939563075, 0.59929893943920431, 0, 0.017646908496911137},
-  {0.09132360789979399, 0.69310764313735118, 0, 0.014292321640314826},
-  {0.01777991514736349, 0.74920428655673188, 0, 0.0069879417037127843},
-  {0.95536604471003006, 0.040096165611933805, 0, 0.00036639404082459889},
-  {0.85563374295785444, 0.12968900724865093, 0, 0.001983961575144539},
-  {0.71317524285556955, 0.25766421302685144, 0, 0.0050524214381561664},
-  {0.54518668480342669, 0.4085739184475205, 0, 0.0088062444316974395},
-  {0.37193216458327227, 0.56421421271748695, 0, 0.011791460746205698},
-  {0.21430847939563075, 0.70581280832900417, 0, 0.012509578034169922},
-  {0.09132360789979399, 0.81629420625180038, 0, 0.010131571367317327},
-  {0.01777991514736349, 0.88236094994855019, 0, 0.0049536269798263225},
-  {0.95536604471003006, 0.04374774490514631, 0, 0.00016678370324769984},
-  {0.85563374295785444, 0.14149985465011697, 0, 0.0009031054595185176},
-  {0.71317524285556955, 0.28112983101129813, 0, 0.0022998779017455581},
-  {0.54518668480342669, 0.44578296418992969, 0, 0.0040086297656954876},
-  {0.37193216458327227, 0.61559750347988773, 0, 0.0053675094865790664},
-  {0.21430847939563075, 0.77009155908843507, 0, 0.0056943987023078914},
-  {0.09132360789979399, 0.89063455713640582, 0, 0.004611922695458035},
-  {0.01777991514736349, 0.96271803459238636, 0, 0.0022549063580394471},
-  {0.96374218711679061, 0.00057722003908934822, 0, 8.8623506503160345e-05},
-  {0.88192102121000127, 0.0018798032019288295, 0, 0.00049008473594191516},
-  {0.76282301518503959, 0.0037758291954058721, 0, 0.0012924587068171439},
-  {0.618117234695294, 0.0060795278917336387, 0, 0.0023732607135995335},
-  {0.46197040108101095, 0.0085653667836943052, 0, 0.0034280855055771348},
-  {0.30966757992763783, 0.010990009457612434, 0, 0.0040762685572341304},
-  {0.17611665616299527, 0.01311612417071319, 0, 0.0040041348140169523},
-  {0.074387389709196061, 0.014735641910190117, 0, 0.0030914442770354402},
-  {0.014412409648876523, 0.015690436410517854, 0, 0.0014742362736666883},
-  {0.96374218711679061, 0.0029725767146089399, 0, 0.00019698300740082799},
-  {0.88192102121000127, 0.0096806397000988708, 0, 0.0010893087960092904},
-  {0.76282301518503959, 0.019444823783858176, 0, 0.002872741251793588},
-  {0.618117234695294, 0.03130844707902742, 0, 0.0052750342562263696},
-  {0.46197040108101095, 0.044110058780120427, 0, 0.0076195878402948473},
-  {0.30966757992763783, 0.056596521247894431, 0, 0.0090603009411366446},
-  {0.17611665616299527, 0.06754561979049109, 0, 0.0088999696449077806},
-  {0.074387389709196061, 0.075885837376942628, 0, 0.0068713371308638492},
-  {0.014412409648876523, 0.080802852911241466, 0, 0.0032767773050810015},
-  {0.96374218711679061, 0.0070091531242226605, 0, 0.00028417603888582384},
-  {0.88192102121000127, 0.022826353198877287, 0, 0.0015714830576401527},
-  {0.76282301518503959, 0.045849698917700979, 0, 0.0041443383388773125},
-  {0.618117234695294, 0.073823393213047567, 0, 0.0076099880883184054},
-  {0.46197040108101095, 0.10400880649736234, 0, 0.010992340501693839},
-  {0.30966757992763783, 0.13345111726645575, 0, 0.013070774309616366},
-  {0.17611665616299527, 0.15926841842477399, 0, 0.01283947358336115},
-  {0.074387389709196061, 0.17893413869550012, 0, 0.0099128823011855518},
-  {0.014412409648876523, 0.19052815900276612, 0, 0.0047272178811550098},
-  {0.96374218711679061, 0.012250546465347009, 0, 0.00034059060635622184},
-  {0.88192102121000127, 0.039895732842657947, 0, 0.0018834535437213082},
-  {0.76282301518503959, 0.080135767768058142, 0, 0.0049670715142548748},
-  {0.618117234695294, 0.12902798565787085, 0, 0.0091207213230435676},
-  {0.46197040108101095, 0.18178582978846428, 0, 0.013174537626130325},
-  {0.30966757992763783, 0.23324488478863117, 0, 0.015665581676455844},
-  {0.17611665616299527, 0.27836817455623925, 0, 0.015388363178672678},
-  {0.074387389709196061, 0.31273977632913752, 0, 0.011880785610693761},
-  {0.014412409648876523, 0.33300372005773038, 0, 0.0056656641806716252},
-  {0.96374218711679061, 0.018128906441604697, 0, 0.00036010076748104765},
-  {0.88192102121000127, 0.059039489394999367, 0, 0.0019913440181599774},
-  {0.76282301518503959, 0.11858849240748021, 0, 0.0052516018675679331},
-  {0.618117234695294, 0.190941382652353, 0, 0.0096431865327889603},
-  {0.46197040108101095, 0.26901479945949452, 0, 0.013929218897527599},
-  {0.30966757992763783, 0.34516621003618109, 0, 0.016562958224481089},
-  {0.17611665616299527, 0.41194167191850239, 0, 0.016269859730427928},
-  {0.074387389709196061, 0.462806305145402, 0, 0.012561356469749435},
-  {0.014412409648876523, 0.49279379517556177, 0, 0.0059902122421306254},
-  {0.96374218711679061, 0.024007266417862386, 0, 0.00034059060635622184},
-  {0.88192102121000127, 0.078183245947340788, 0, 0.0018834535437213082},
-  {0.76282301518503959, 0.15704121704690227, 0, 0.0049670715142548748},
-  {0.618117234695294, 0.25285477964683511, 0, 0.0091207213230435676},
-  {0.46197040108101095, 0.3562437691305248, 0, 0.013174537626130325},
-  {0.30966757992763783, 0.45708753528373097, 0, 0.015665581676455844},
-  {0.17611665616299527, 0.54551516928076549, 0, 0.015388363178672678},
-  {0.074387389709196061, 0.61287283396166647, 0, 0.011880785610693761},
-  {0.014412409648876523, 0.65258387029339315, 0, 0.0056656641806716252},
-  {0.96374218711679061, 0.029248659758986731, 0, 0.00028417603888582384},
-  {0.88192102121000127, 0.095252625591121437, 0, 0.0015714830576401527},
-  {0.76282301518503959, 0.19132728589725942, 0, 0.0041443383388773125},
-  {0.618117234695294, 0.3080593720916584, 0, 0.0076099880883184054},
-  {0.46197040108101095, 0.43402079242162667, 0, 0.010992340501693839},
-  {0.30966757992763783, 0.55688130280590642, 0, 0.013070774309616366},
-  {0.17611665616299527, 0.66461492541223077, 0, 0.01283947358336115},
-  {0.074387389709196061, 0.74667847159530387, 0, 0.0099128823011855518},
-  {0.014412409648876523, 0.79505943134835733, 0, 0.0047272178811550098},
-  {0.96374218711679061, 0.033285236168600456, 0, 0.00019698300740082799},
-  {0.88192102121000127, 0.10839833908989986, 0, 0.0010893087960092904},
-  {0.76282301518503959, 0.21773216103110221, 0, 0.002872741251793588},
-  {0.618117234695294, 0.35057431822567858, 0, 0.0052750342562263696},
-  {0.46197040108101095, 0.49391954013886857, 0, 0.0076195878402948473},
-  {0.30966757992763783, 0.63373589882446768, 0, 0.0090603009411366446},
-  {0.17611665616299527, 0.75633772404651367, 0, 0.0088999696449077806},
-  {0.074387389709196061, 0.84972677291386134, 0, 0.0068713371308638492},
-  {0.014412409648876523, 0.90478473743988197, 0, 0.0032767773050810015},
-  {0.96374218711679061, 0.035680592844120049, 0, 8.8623506503160345e-05},
-  {0.88192102121000127, 0.1161991755880699, 0, 0.00049008473594191516},
-  {0.76282301518503959, 0.23340115561955455, 0, 0.0012924587068171439},
-  {0.618117234695294, 0.37580323741297234, 0, 0.0023732607135995335},
-  {0.46197040108101095, 0.5294642321352947, 0, 0.0034280855055771348},
-  {0.30966757992763783, 0.67934241061474976, 0, 0.0040762685572341304},
-  {0.17611665616299527, 0.81076721966629162, 0, 0.0040041348140169523},
-  {0.074387389709196061, 0.91087696838061383, 0, 0.0030914442770354402},
-  {0.014412409648876523, 0.96989715394060572, 0, 0.0014742362736666883},
-};
-#define NGSX_RULE_TET_MAXORDER 8
-#define NGSX_RULE_TET_NPTS 301
-static const int NGSX_RULE_TET_OFFS[10] = {0, 1, 2, 6, 20, 34, 48, 112, 176, 301};
-static const double NGSX_RULE_TET_DATA[301][4] = {
-  {0.25, 0.25, 0.25, 0.16666666666666666},
-  {0.25, 0.25, 0.25, 0.16666666666666666},
-  {0.58541019662496896, 0.138196601125011, 0.138196601125011, 0.041666666666666664},
-  {0.138196601125011, 0.58541019662496896, 0.138196601125011, 0.041666666666666664},
-  {0.138196601125011, 0.138196601125011, 0.58541019662496896, 0.041666666666666664},
-  {0.138196601125011, 0.138196601125011, 0.138196601125011, 0.041666666666666664},
-  {0.45449629587434998, 0.45449629587434998, 0.045503704125650003, 0.0070910034628469997},
-  {0.45449629587434998, 0.045503704125650003, 0.45449629587434998, 0.0070910034628469997},
-  {0.45449629587434998, 0.045503704125650003, 0.045503704125650003, 0.0070910034628469997},
-  {0.045503704125650003, 0.45449629587434998, 0.45449629587434998, 0.0070910034628469997},
-  {0.045503704125650003, 0.45449629587434998, 0.045503704125650003, 0.0070910034628469997},
-  {0.045503704125650003, 0.045503704125650003, 0.45449629587434998, 0.0070910034628469997},
-  {0.310885919263301, 0.310885919263301, 0.310885919263301, 0.018781320953003},
-  {0.067342242210098005, 0.310885919263301, 0.310885919263301, 0.018781320953003},
-  {0.310885919263301, 0.067342242210098005, 0.310885919263301, 0.018781320953003},
-  {0.310885919263301, 0.310885919263301, 0.067342242210098005, 0.018781320953003},
-  {0.092735250310890999, 0.092735250310890999, 0.092735250310890999, 0.012248840519394},
-  {0.72179424906732603, 0.092735250310890999, 0.092735250310890999, 0.012248840519394},
-  {0.092735250310890999, 0.72179424906732603, 0.092735250310890999, 0.012248840519394},
-  {0.092735250310890999, 0.092735250310890999, 0.72179424906732603, 0.012248840519394},
-  {0.45449629587434998, 0.45449629587434998, 0.045503704125650003, 0.0070910034628469997},
-  {0.45449629587434998, 0.045503704125650003, 0.45449629587434998, 0.0070910034628469997},
-  {0.45449629587434998, 0.045503704125650003, 0.045503704125650003, 0.0070910034628469997},
-  {0.045503704125650003, 0.45449629587434998, 0.45449629587434998, 0.0070910034628469997},
-  {0.045503704125650003, 0.45449629587434998, 0.045503704125650003, 0.0070910034628469997},
-  {0.045503704125650003, 0.045503704125650003, 0.45449629587434998, 0.0070910034628469997},
-  {0.310885919263301, 0.310885919263301, 0.310885919263301, 0.018781320953003},
-  {0.067342242210098005, 0.310885919263301, 0.310885919263301, 0.018781320953003},
-  {0.310885919263301, 0.067342242210098005, 0.310885919263301, 0.018781320953003},
-  {0.310885919263301, 0.310885919263301, 0.067342242210098005, 0.018781320953003},
-  {0.092735250310890999, 0.092735250310890999, 0.092735250310890999, 0.012248840519394},
-  {0.72179424906732603, 0.092735250310890999, 0.092735250310890999, 0.012248840519394},
-  {0.092735250310890999, 0.72179424906732603, 0.092735250310890999, 0.012248840519394},
-  {0.092735250310890999, 0.092735250310890999, 0.72179424906732603, 0.012248840519394},
-  {0.45449629587434998, 0.45449629587434998, 0.045503704125650003, 0.0070910034628469997},
-  {0.45449629587434998, 0.045503704125650003, 0.45449629587434998, 0.0070910034628469997},
-  {0.45449629587434998, 0.045503704125650003, 0.045503704125650003, 0.0070910034628469997},
-  {0.045503704125650003, 0.45449629587434998, 0.45449629587434998, 0.0070910034628469997},
-  {0.045503704125650003, 0.45449629587434998, 0.045503704125650003, 0.0070910034628469997},
-  {0.045503704125650003, 0.045503704125650003, 0.45449629587434998, 0.0070910034628469997},
-  {0.310885919263301, 0.310885919263301, 0.310885919263301, 0.018781320953003},
-  {0.067342242210098005, 0.310885919263301, 0.310885919263301, 0.018781320953003},
-  {0.310885919263301, 0.067342242210098005, 0.310885919263301, 0.018781320953003},
-  {0.310885919263301, 0.310885919263301, 0.067342242210098005, 0.018781320953003},
-  {0.092735250310890999, 0.092735250310890999, 0.092735250310890999, 0.012248840519394},
-  {0.72179424906732603, 0.092735250310890999, 0.092735250310890999, 0.012248840519394},
-  {0.092735250310890999, 0.72179424906732603, 0.092735250310890999, 0.012248840519394},
-  {0.092735250310890999, 0.092735250310890999, 0.72179424906732603, 0.012248840519394},
-  {0.79585141789677283, 0.17561680396250501, 0.0019810139747004326, 5.6142540266950073e-05},
-  {0.51704729510436753, 0.41545530037495704, 0.0046864692747846321, 0.00037221707525625651},
-  {0.23860073755186229, 0.65498620481693148, 0.0073884548386119759, 0.00077800942593168052},
-  {0.048500549446997387, 0.81851801642053323, 0.009233146216573623, 0.00060137292872016433},
-  {0.79585141789677283, 0.11913915929712367, 0.0059023610000580994, 0.00023379551527909074},
-  {0.51704729510436753, 0.28184657786378003, 0.013963169280339019, 0.0015500310903537975},
-  {0.23860073755186229, 0.44434532477748306, 0.022013639604288232, 0.0032398803788143632},
-  {0.048500549446997387, 0.55528597574701355, 0.027509832253848281, 0.0025043094430088342},
-  {0.79585141789677283, 0.056517108699407355, 0.010250325460829475, 0.00036634579855542314},
-  {0.51704729510436753, 0.13370208226799035, 0.024249114818074013, 0.0024288206593849064},
-  {0.23860073755186229, 0.21078806639798719, 0.038229950780567068, 0.0050767293939916963},
-  {0.048500549446997387, 0.26341597536611217, 0.047774904647816904, 0.0039241267807629699},
-  {0.79585141789677283, 0.011657740668923408, 0.013364994112965895, 0.00024398542162060074},
-  {0.51704729510436753, 0.027578625974397, 0.031617462101731879, 0.0016175887234344795},
-  {0.23860073755186229, 0.043479092804287606, 0.049846521368884254, 0.0033810895785648543},
-  {0.048500549446997387, 0.054334611227234521, 0.062291809348452673, 0.0026134590075073505},
-  {0.79585141789677283, 0.17561680396250501, 0.0094157572165539279, 0.00010525391877839163},
-  {0.51704729510436753, 0.41545530037495704, 0.022274783246233512, 0.00069781854580626011},
-  {0.23860073755186229, 0.65498620481693148, 0.035117317623346654, 0.001458582752694613},
-  {0.048500549446997387, 0.81851801642053323, 0.043885133689350792, 0.0011274313042136642},
-  {0.79585141789677283, 0.11913915929712367, 0.028053915262969079, 0.00043831102153430313},
-  {0.51704729510436753, 0.28184657786378003, 0.066366928046127288, 0.0029059398757580184},
-  {0.23860073755186229, 0.44434532477748306, 0.10463080453434877, 0.0060740056403215002},
-  {0.048500549446997387, 0.55528597574701355, 0.13075420207953334, 0.0046949849696341561},
-  {0.79585141789677283, 0.056517108699407355, 0.048719785505009605, 0.00068681129750476546},
-  {0.51704729510436753, 0.13370208226799035, 0.11525601573701777, 0.0045534614428672385},
-  {0.23860073755186229, 0.21078806639798719, 0.18170691350375726, 0.0095176609528948106},
-  {0.048500549446997387, 0.26341597536611217, 0.22707406860967841, 0.0073568050090829055},
-  {0.79585141789677283, 0.011657740668923408, 0.063523802141471034, 0.00045741467393992975},
-  {0.51704729510436753, 0.027578625974397, 0.15027776217405056, 0.0030325943803693883},
-  {0.23860073755186229, 0.043479092804287606, 0.23692046057885846, 0.0063387393265891545},
-  {0.048500549446997387, 0.054334611227234521, 0.29607290049207674, 0.0048996144598887443},
-  {0.79585141789677283, 0.17561680396250501, 0.019116020924168239, 0.00010525391877839163},
-  {0.51704729510436753, 0.41545530037495704, 0.045222621274441946, 0.00069781854580626011},
-  {0.23860073755186229, 0.65498620481693148, 0.071295740007859612, 0.001458582752694613},
-  {0.048500549446997387, 0.81851801642053323, 0.089096300443118545, 0.0011274313042136642},
-  {0.79585141789677283, 0.11913915929712367, 0.056955507543134429, 0.00043831102153430313},
-  {0.51704729510436753, 0.28184657786378003, 0.13473919898572514, 0.0029059398757580184},
-  {0.23860073755186229, 0.44434532477748306, 0.21242313313630587, 0.0060740056403215002},
-  {0.048500549446997387, 0.55528597574701355, 0.26545927272645564, 0.0046949849696341561},
-  {0.79585141789677283, 0.056517108699407355, 0.098911687898810205, 0.00068681129750476546},
-  {0.51704729510436753, 0.13370208226799035, 0.23399460689062435, 0.0045534614428672385},
-  {0.23860073755186229, 0.21078806639798719, 0.36890428254639329, 0.0095176609528948106},
-  {0.048500549446997387, 0.26341597536611217, 0.46100940657721196, 0.0073568050090829055},
-  {0.79585141789677283, 0.011657740668923408, 0.12896703929283271, 0.00045741467393992975},
-  {0.51704729510436753, 0.027578625974397, 0.30509631674718485, 0.0030325943803693883},
-  {0.23860073755186229, 0.043479092804287606, 0.48099970906499162, 0.0063387393265891545},
-  {0.048500549446997387, 0.054334611227234521, 0.60109193883369127, 0.0048996144598887443},
-  {0.79585141789677283, 0.17561680396250501, 0.026550764166021736, 5.6142540266950073e-05},
-  {0.51704729510436753, 0.41545530037495704, 0.06281093524589082, 0.00037221707525625651},
-  {0.23860073755186229, 0.65498620481693148, 0.099024602792594285, 0.00077800942593168052},
-  {0.048500549446997387, 0.81851801642053323, 0.1237482879158957, 0.00060137292872016433},
-  {0.79585141789677283, 0.11913915929712367, 0.079107061806045403, 0.00023379551527909074},
-  {0.51704729510436753, 0.28184657786378003, 0.18714295775151338, 0.0015500310903537975},
-  {0.23860073755186229, 0.44434532477748306, 0.29504029806636639, 0.0032398803788143632},
-  {0.048500549446997387, 0.55528597574701355, 0.36870364255214072, 0.0025043094430088342},
-  {0.79585141789677283, 0.056517108699407355, 0.13738114794299033, 0.00036634579855542314},
-  {0.51704729510436753, 0.13370208226799035, 0.32500150780956805, 0.0024288206593849064},
-  {0.23860073755186229, 0.21078806639798719, 0.5123812452695834, 0.0050767293939916963},
-  {0.048500549446997387, 0.26341597536611217, 0.64030857053907342, 0.0039241267807629699},
-  {0.79585141789677283, 0.011657740668923408, 0.17912584732133785, 0.00024398542162060074},
-  {0.51704729510436753, 0.027578625974397, 0.4237566168195035, 0.0016175887234344795},
-  {0.23860073755186229, 0.043479092804287606, 0.66807364827496585, 0.0033810895785648543},
-  {0.048500549446997387, 0.054334611227234521, 0.83487302997731527, 0.0026134590075073505},
-  {0.79585141789677283, 0.17561680396250501, 0.0019810139747004326, 5.6142540266950073e-05},
-  {0.51704729510436753, 0.41545530037495704, 0.0046864692747846321, 0.00037221707525625651},
-  {0.23860073755186229, 0.65498620481693148, 0.0073884548386119759, 0.00077800942593168052},
-  {0.048500549446997387, 0.81851801642053323, 0.009233146216573623, 0.00060137292872016433},
-  {0.79585141789677283, 0.11913915929712367, 0.0059023610000580994, 0.00023379551527909074},
-  {0.51704729510436753, 0.28184657786378003, 0.013963169280339019, 0.0015500310903537975},
-  {0.23860073755186229, 0.44434532477748306, 0.022013639604288232, 0.0032398803788143632},
-  {0.048500549446997387, 0.55528597574701355, 0.027509832253848281, 0.0025043094430088342},
-  {0.79585141789677283, 0.056517108699407355, 0.010250325460829475, 0.00036634579855542314},
-  {0.51704729510436753, 0.13370208226799035, 0.024249114818074013, 0.0024288206593849064},
-  {0.23860073755186229, 0.21078806639798719, 0.038229950780567068, 0.0050767293939916963},
-  {0.048500549446997387, 0.26341597536611217, 0.047774904647816904, 0.0039241267807629699},
-  {0.79585141789677283, 0.011657740668923408, 0.013364994112965895, 0.00024398542162060074},
-  {0.51704729510436753, 0.027578625974397, 0.031617462101731879, 0.0016175887234344795},
-  {0.23860073755186229, 0.043479092804287606, 0.049846521368884254, 0.0033810895785648543},
-  {0.048500549446997387, 0.054334611227234521, 0.062291809348452673, 0.0026134590075073505},
-  {0.79585141789677283, 0.17561680396250501, 0.0094157572165539279, 0.00010525391877839163},
-  {0.51704729510436753, 0.41545530037495704, 0.022274783246233512, 0.00069781854580626011},
-  {0.23860073755186229, 0.65498620481693148, 0.035117317623346654, 0.001458582752694613},
-  {0.048500549446997387, 0.81851801642053323, 0.043885133689350792, 0.0011274313042136642},
-  {0.79585141789677283, 0.11913915929712367, 0.028053915262969079, 0.00043831102153430313},
-  {0.51704729510436753, 0.28184657786378003, 0.066366928046127288, 0.0029059398757580184},
-  {0.23860073755186229, 0.44434532477748306, 0.10463080453434877, 0.0060740056403215002},
-  {0.048500549446997387, 0.55528597574701355, 0.13075420207953334, 0.0046949849696341561},
-  {0.79585141789677283, 0.056517108699407355, 0.048719785505009605, 0.00068681129750476546},
-  {0.51704729510436753, 0.13370208226799035, 0.11525601573701777, 0.0045534614428672385},
-  {0.23860073755186229, 0.21078806639798719, 0.18170691350375726, 0.0095176609528948106},
-  {0.048500549446997387, 0.26341597536611217, 0.22707406860967841, 0.0073568050090829055},
-  {0.79585141789677283, 0.011657740668923408, 0.063523802141471034, 0.00045741467393992975},
-  {0.51704729510436753, 0.027578625974397, 0.15027776217405056, 0.0030325943803693883},
-  {0.23860073755186229, 0.043479092804287606, 0.23692046057885846, 0.0063387393265891545},
-  {0.048500549446997387, 0.054334611227234521, 0.29607290049207674, 0.0048996144598887443},
-  {0.79585141789677283, 0.17561680396250501, 0.019116020924168239, 0.00010525391877839163},
-  {0.51704729510436753, 0.41545530037495704, 0.045222621274441946, 0.00069781854580626011},
-  {0.23860073755186229, 0.65498620481693148, 0.071295740007859612, 0.001458582752694613},
-  {0.048500549446997387, 0.81851801642053323, 0.089096300443118545, 0.0011274313042136642},
-  {0.79585141789677283, 0.11913915929712367, 0.056955507543134429, 0.00043831102153430313},
-  {0.51704729510436753, 0.28184657786378003, 0.13473919898572514, 0.0029059398757580184},
-  {0.23860073755186229, 0.44434532477748306, 0.21242313313630587, 0.0060740056403215002},
-  {0.048500549446997387, 0.55528597574701355, 0.26545927272645564, 0.0046949849696341561},
-  {0.79585141789677283, 0.056517108699407355, 0.098911687898810205, 0.00068681129750476546},
-  {0.51704729510436753, 0.13370208226799035, 0.23399460689062435, 0.0045534614428672385},
-  {0.23860073755186229, 0.21078806639798719, 0.36890428254639329, 0.0095176609528948106},
-  {0.048500549446997387, 0.26341597536611217, 0.46100940657721196, 0.0073568050090829055},
-  {0.79585141789677283, 0.011657740668923408, 0.12896703929283271, 0.00045741467393992975},
-  {0.51704729510436753, 0.027578625974397, 0.30509631674718485, 0.0030325943803693883},
-  {0.23860073755186229, 0.043479092804287606, 0.48099970906499162, 0.0063387393265891545},
-  {0.048500549446997387, 0.054334611227234521, 0.60109193883369127, 0.0048996144598887443},
-  {0.79585141789677283, 0.17561680396250501, 0.026550764166021736, 5.6142540266950073e-05},
-  {0.51704729510436753, 0.41545530037495704, 0.06281093524589082, 0.00037221707525625651},
-  {0.23860073755186229, 0.65498620481693148, 0.099024602792594285, 0.00077800942593168052},
-  {0.048500549446997387, 0.81851801642053323, 0.1237482879158957, 0.00060137292872016433},
-  {0.79585141789677283, 0.11913915929712367, 0.079107061806045403, 0.00023379551527909074},
-  {0.51704729510436753, 0.28184657786378003, 0.18714295775151338, 0.0015500310903537975},
-  {0.23860073755186229, 0.44434532477748306, 0.29504029806636639, 0.0032398803788143632},
-  {0.048500549446997387, 0.55528597574701355, 0.36870364255214072, 0.0025043094430088342},
-  {0.79585141789677283, 0.056517108699407355, 0.13738114794299033, 0.00036634579855542314},
-  {0.51704729510436753, 0.13370208226799035, 0.32500150780956805, 0.0024288206593849064},
-  {0.23860073755186229, 0.21078806639798719, 0.5123812452695834, 0.0050767293939916963},
-  {0.048500549446997387, 0.26341597536611217, 0.64030857053907342, 0.0039241267807629699},
-  {0.79585141789677283, 0.011657740668923408, 0.17912584732133785, 0.00024398542162060074},
-  {0.51704729510436753, 0.027578625974397, 0.4237566168195035, 0.0016175887234344795},
-  {0.23860073755186229, 0.043479092804287606, 0.66807364827496585, 0.0033810895785648543},
-  {0.048500549446997387, 0.054334611227234521, 0.83487302997731527, 0.0026134590075073505},
-  {0.85105421294701644, 0.13426940114634409, 0.00068847039341226777, 7.674555521796361e-06},
-  {0.6343334726308868, 0.32963554472103873, 0.0016902161715118362, 5.9801395389279327e-05},
-  {0.38988638706551931, 0.54999601573694956, 0.0028201211154348519, 0.00016640755405275399},
-  {0.17348032077169573, 0.74507849172112484, 0.0038204123794308657, 0.00023543074683006317},
-  {0.03457893991821509, 0.87029321309463237, 0.0044624546299289304, 0.0001525364704985861},
-  {0.85105421294701644, 0.10358647356188862, 0.0021278088899254828, 3.6018593201297179e-05},
-  {0.6343334726308868, 0.2543080057465078, 0.0052238368273377304, 0.00028066278591365375},
-  {0.38988638706551931, 0.42431222048264011, 0.0087159576323212178, 0.0007809919386244892},
-  {0.17348032077169573, 0.57481490812699298, 0.011807490201349174, 0.0011049349077045664},
-  {0.03457893991821509, 0.67141585603007559, 0.013791806769482957, 0.00071589150194384691},
-  {0.85105421294701644, 0.065234502821678059, 0.0039269027916266864, 7.1339926217053483e-05},
-  {0.6343334726308868, 0.16015272793830798, 0.0096406681621643286, 0.00055589240609851581},
-  {0.38988638706551931, 0.26721439385432638, 0.016085428780805947, 0.0015468651695030125},
-  {0.17348032077169573, 0.36199479967574705, 0.021790897882472241, 0.0021884801094189236},
-  {0.03457893991821509, 0.42283010559815015, 0.025452983470970993, 0.0014179245325508813},
-  {0.85105421294701644, 0.02949326437223589, 0.0056035270404614923, 8.1470536312881737e-05},
-  {0.6343334726308868, 0.072406878886331391, 0.01375683270031392, 0.00063483178156523309},
-  {0.38988638706551931, 0.12081068178837213, 0.022953238191395602, 0.0017665274082243406},
-  {0.17348032077169573, 0.16366198662379478, 0.031094705420448402, 0.0024992547326438477},
-  {0.03457893991821509, 0.19116632379395626, 0.036320349320621594, 0.0016192765852692755},
-  {0.85105421294701644, 0.0059295104909977848, 0.0067089045501620738, 4.7165336505935231e-05},
-  {0.6343334726308868, 0.014557132183071392, 0.016470568774368477, 0.00036752003800731445},
-  {0.38988638706551931, 0.024288535716076826, 0.027481099498812365, 0.0010226870157805093},
-  {0.17348032077169573, 0.032903630280304623, 0.037228589988925066, 0.0014468812384700104},
-  {0.03457893991821509, 0.03843327439633331, 0.043485068432992914, 0.00093743982176696739},
-  {0.85105421294701644, 0.13426940114634409, 0.0033868012563232708, 1.5503780017197856e-05},
-  {0.6343334726308868, 0.32963554472103873, 0.0083147021395679876, 0.00012080799678934922},
-  {0.38988638706551931, 0.54999601573694956, 0.013873058054682572, 0.00033616879881924152},
-  {0.17348032077169573, 0.74507849172112484, 0.018793803728000477, 0.00047560624166069498},
-  {0.03457893991821509, 0.87029321309463237, 0.021952210424070785, 0.00030814708115582521},
-  {0.85105421294701644, 0.10358647356188862, 0.010467357624338822, 7.2763086270713576e-05},
-  {0.6343334726308868, 0.2543080057465078, 0.025697687655046146, 0.00056698190266016605},
-  {0.38988638706551931, 0.42431222048264011, 0.042876522420811337, 0.0015777235798542779},
-  {0.17348032077169573, 0.57481490812699298, 0.058084738328039655, 0.0022321380949974143},
-  {0.03457893991821509, 0.67141585603007559, 0.06784621232925242, 0.001446210706378584},
-  {0.85105421294701644, 0.065234502821678059, 0.019317663381606839, 0.00014411759995364994},
-  {0.6343334726308868, 0.16015272793830798, 0.047425462817050901, 0.0011229879766854452},
-  {0.38988638706551931, 0.26721439385432638, 0.079129256573143056, 0.0031249050496968359},
-  {0.17348032077169573, 0.36199479967574705, 0.10719624406648309, 0.0044210657010794888},
-  {0.03457893991821509, 0.42283010559815015, 0.12521118877662393, 0.0028644251737084863},
-  {0.85105421294701644, 0.02949326437223589, 0.027565502601231005, 0.00016458298715681162},
-  {0.6343334726308868, 0.072406878886331391, 0.067674163941211576, 0.0012824576304595445},
-  {0.38988638706551931, 0.12081068178837213, 0.11291415968958744, 0.0035686564848839944},
-  {0.17348032077169573, 0.16366198662379478, 0.15296458408475713, 0.0050488781365648711},
-  {0.03457893991821509, 0.19116632379395626, 0.17867116129643199, 0.0032711872229882494},
-  {0.85105421294701644, 0.0059295104909977848, 0.033003200393884859, 9.5281218508139965e-05},
-  {0.6343334726308868, 0.014557132183071392, 0.081023880694295114, 0.00074244688242790843},
-  {0.38988638706551931, 0.024288535716076826, 0.13518812602300068, 0.0020659847302002855},
-  {0.17348032077169573, 0.032903630280304623, 0.18313908129108611, 0.0029229221638361687},
-  {0.03457893991821509, 0.03843327439633331, 0.21391665612550584, 0.0018937723148603053},
-  {0.85105421294701644, 0.13426940114634409, 0.0073381929533197316, 1.8427496577585656e-05},
-  {0.6343334726308868, 0.32963554472103873, 0.01801549132403724, 0.0001435900757693459},
-  {0.38988638706551931, 0.54999601573694956, 0.030058798598765511, 0.00039956380849450986},
-  {0.17348032077169573, 0.74507849172112484, 0.040720593753589725, 0.00056529648774421108},
-  {0.03457893991821509, 0.87029321309463237, 0.04756392349357632, 0.00036625773050785873},
-  {0.85105421294701644, 0.10358647356188862, 0.02267965674554747, 8.6484813493276533e-05},
-  {0.6343334726308868, 0.2543080057465078, 0.055679260811302714, 0.00067390385178540415},
-  {0.38988638706551931, 0.42431222048264011, 0.09290069622592026, 0.0018752520892253745},
-  {0.17348032077169573, 0.57481490812699298, 0.12585238555065564, 0.0026530766729556386},
-  {0.03457893991821509, 0.67141585603007559, 0.14700260202585469, 0.0017189384016476643},
-  {0.85105421294701644, 0.065234502821678059, 0.04185564211565275, 0.00017129542453323183},
-  {0.6343334726308868, 0.16015272793830798, 0.10275689971540261, 0.001334762043455585},
-  {0.38988638706551931, 0.26721439385432638, 0.17144960954007712, 0.0037142024102955699},
-  {0.17348032077169573, 0.36199479967574705, 0.23226243977627861, 0.0052547941847441325},
-  {0.03457893991821509, 0.42283010559815015, 0.27129547724181741, 0.0034046010087031343},
-  {0.85105421294701644, 0.02949326437223589, 0.059726261340373836, 0.00019562019257218056},
-  {0.6343334726308868, 0.072406878886331391, 0.1466298242413909, 0.0015243046257091557},
-  {0.38988638706551931, 0.12081068178837213, 0.24465146557305426, 0.0042416368839619497},
-  {0.17348032077169573, 0.16366198662379478, 0.33142884630225472, 0.0060010000450852544},
-  {0.03457893991821509, 0.19116632379395626, 0.38712736814391435, 0.0038880706053227923},
-  {0.85105421294701644, 0.0059295104909977848, 0.071508138280992881, 0.00011324943504224728},
-  {0.6343334726308868, 0.014557132183071392, 0.17555469759302089, 0.00088245817276838502},
-  {0.38988638706551931, 0.024288535716076826, 0.29291253860920191, 0.0024555899595375521},
-  {0.17348032077169573, 0.032903630280304623, 0.39680802447399982, 0.003474129413013644},
-  {0.03457893991821509, 0.03843327439633331, 0.46349389284272585, 0.0022509015744614572},
-  {0.85105421294701644, 0.13426940114634409, 0.011289584650316192, 1.5503780017197856e-05},
-  {0.6343334726308868, 0.32963554472103873, 0.02771628050850649, 0.00012080799678934922},
-  {0.38988638706551931, 0.54999601573694956, 0.046244539142848443, 0.00033616879881924152},
-  {0.17348032077169573, 0.74507849172112484, 0.062647383779178958, 0.00047560624166069498},
-  {0.03457893991821509, 0.87029321309463237, 0.073175636563081847, 0.00030814708115582521},
-  {0.85105421294701644, 0.10358647356188862, 0.034891955866756114, 7.2763086270713576e-05},
-  {0.6343334726308868, 0.2543080057465078, 0.085660833967559274, 0.00056698190266016605},
-  {0.38988638706551931, 0.42431222048264011, 0.14292487003102916, 0.0015777235798542779},
-  {0.17348032077169573, 0.57481490812699298, 0.19362003277327161, 0.0022321380949974143},
-  {0.03457893991821509, 0.67141585603007559, 0.22615899172245696, 0.001446210706378584},
-  {0.85105421294701644, 0.065234502821678059, 0.064393620849698657, 0.00014411759995364994},
-  {0.6343334726308868, 0.16015272793830798, 0.15808833661375429, 0.0011229879766854452},
-  {0.38988638706551931, 0.26721439385432638, 0.26376996250701118, 0.0031249050496968359},
-  {0.17348032077169573, 0.36199479967574705, 0.35732863548607408, 0.0044210657010794888},
-  {0.03457893991821509, 0.42283010559815015, 0.41737976570701085, 0.0028644251737084863},
-  {0.85105421294701644, 0.02949326437223589, 0.091887020079516657, 0.00016458298715681162},
-  {0.6343334726308868, 0.072406878886331391, 0.22558548454157024, 0.0012824576304595445},
-  {0.38988638706551931, 0.12081068178837213, 0.376388771456521, 0.0035686564848839944},
-  {0.17348032077169573, 0.16366198662379478, 0.50989310851975223, 0.0050488781365648711},
-  {0.03457893991821509, 0.19116632379395626, 0.59558357499139669, 0.0032711872229882494},
-  {0.85105421294701644, 0.0059295104909977848, 0.1100130761681009, 9.5281218508139965e-05},
-  {0.6343334726308868, 0.014557132183071392, 0.27008551449174667, 0.00074244688242790843},
-  {0.38988638706551931, 0.024288535716076826, 0.45063695119540309, 0.0020659847302002855},
-  {0.17348032077169573, 0.032903630280304623, 0.61047696765691351, 0.0029229221638361687},
-  {0.03457893991821509, 0.03843327439633331, 0.71307112955994578, 0.0018937723148603053},
-  {0.85105421294701644, 0.13426940114634409, 0.013987915513227195, 7.674555521796361e-06},
-  {0.6343334726308868, 0.32963554472103873, 0.034340766476562638, 5.9801395389279327e-05},
-  {0.38988638706551931, 0.54999601573694956, 0.057297476082096163, 0.00016640755405275399},
-  {0.17348032077169573, 0.74507849172112484, 0.077620775127748579, 0.00023543074683006317},
-  {0.03457893991821509, 0.87029321309463237, 0.090665392357223692, 0.0001525364704985861},
-  {0.85105421294701644, 0.10358647356188862, 0.043231504601169451, 3.6018593201297179e-05},
-  {0.6343334726308868, 0.2543080057465078, 0.10613468479526768, 0.00028066278591365375},
-  {0.38988638706551931, 0.42431222048264011, 0.17708543481951927, 0.0007809919386244892},
-  {0.17348032077169573, 0.57481490812699298, 0.23989728089996212, 0.0011049349077045664},
-  {0.03457893991821509, 0.67141585603007559, 0.28021339728222644, 0.00071589150194384691},
-  {0.85105421294701644, 0.065234502821678059, 0.079784381439678809, 7.1339926217053483e-05},
-  {0.6343334726308868, 0.16015272793830798, 0.19587313126864087, 0.00055589240609851581},
-  {0.38988638706551931, 0.26721439385432638, 0.32681379029934832, 0.0015468651695030125},
-  {0.17348032077169573, 0.36199479967574705, 0.44273398167008499, 0.0021884801094189236},
-  {0.03457893991821509, 0.42283010559815015, 0.51713797101266379, 0.0014179245325508813},
-  {0.85105421294701644, 0.02949326437223589, 0.11384899564028617, 8.1470536312881737e-05},
-  {0.6343334726308868, 0.072406878886331391, 0.27950281578246788, 0.00063483178156523309},
-  {0.38988638706551931, 0.12081068178837213, 0.46634969295471285, 0.0017665274082243406},
-  {0.17348032077169573, 0.16366198662379478, 0.6317629871840611, 0.0024992547326438477},
-  {0.03457893991821509, 0.19116632379395626, 0.73793438696720703, 0.0016192765852692755},
-  {0.85105421294701644, 0.0059295104909977848, 0.13630737201182369, 4.7165336505935231e-05},
-  {0.6343334726308868, 0.014557132183071392, 0.33463882641167331, 0.00036752003800731445},
-  {0.38988638706551931, 0.024288535716076826, 0.55834397771959143, 0.0010226870157805093},
-  {0.17348032077169573, 0.032903630280304623, 0.75638745895907455, 0.0014468812384700104},
-  {0.03457893991821509, 0.03843327439633331, 0.88350271725245866, 0.00093743982176696739},
-};
+/* TEST INFRASTRUCTURE: the quadrature tables are data dumped from the compiled reference (tools/gen_rule_tables.py);
+ * one copy lives beside the kernels, the oracle reads the same file. */
+#include "../ngsxfem_b200/csrc/rule_tables.h"
