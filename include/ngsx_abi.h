@@ -229,8 +229,9 @@ int ngsx_integrate(const ngsx_mesh *mesh, const double *lset_v, int dt, int orde
  * :108-163 produces gf): x(xi) = affine map + sum_i coef[el2dof[e][i]] phi_i(xi), phi = scalar H1 basis of `order` (1..2,
  * vertex dofs then edge dofs, as el2dof of the H1 space), coef interleaved [ndof][dim] (H1(mesh, order, dim=mesh.dim)).
  * The cut rule stays on the reference element (cutint/straightcutrule.cpp:580-661); measure, mapped gradients, interface
- * weight factor |F^-T n_ref| (:558-576) and the level-set normal are evaluated per rule point; h = |det F|^(1/dim) at the
- * first rule point of the element (specialcf.mesh_size is elementwise constant, xfem/symboliccutbfi.cpp:205-214). */
+ * weight factor |F^-T n_ref| (:558-576), the level-set normal and h = specialcf.mesh_size = |det F|^(1/dim)
+ * (NGS/fem/python_fem.cpp:564-593; not flagged elementwise constant, so xfem/symboliccutbfi.cpp:205-214 evaluates it at every
+ * point) are evaluated per rule point. */
 typedef struct ngsx_deformation {
   int32_t order;            /* 1 or 2 */
   int32_t nd;               /* dofs per element and component: dim+1 (order 1), 6 / 10 (order 2) */

@@ -8,8 +8,9 @@
 //     (xfem/symboliccutbfi.cpp:142 trafo(*ir), :219-227),
 //   * interface weights carry |F(xi_q)^-T n_ref| per point (cutint/straightcutrule.cpp:558-576),
 //   * the level-set normal grad(lset)/|grad(lset)| is per point,
-//   * specialcf.mesh_size = |det F|^(1/dim) is flagged elementwise constant, so the reference evaluates it at the first point
-//     of the element's rule only (xfem/symboliccutbfi.cpp:205-214).
+//   * specialcf.mesh_size = |det F|^(1/dim) (NGS/fem/python_fem.cpp:564-593) is per point as well: MeshSizeCF is not flagged
+//     elementwise constant, so a coefficient tree containing it takes the cf->Evaluate(mir, val) branch of
+//     xfem/symboliccutbfi.cpp:205-214 (pinned against the compiled reference: oracle/ref_driver.cpp ElmatForm).
 // So there is no constant-rule shortcut: every listed element of the domain takes the quadrature path.
 //
 // Execution model: persistent CTAs of 8 warps, ONE WARP PER ELEMENT.  The warp parks the element's geometry coefficients
@@ -138,14 +139,15 @@ __device__ __forceinline__ void load_iso(const DefArgs &A, int64_t e, int lane, 
 template <int DIM, int ORDER, int DORD>
 __global__ void __launch_bounds__(DW * 32) k_elmat_def(DefArgs A, int64_t count) {
   constexpr int ND = H1<DIM, ORDER>::ND, NE = ND * ND, NDG = H1<DIM, DORD>::ND, T = (NE + 31) / 32;
-  constexpr size_t PER_WARP = (size_t)DQ * ND * 32 + (size_t)DQ * ND * 8 + DQ * 8 + NDG * DIM * 8;
+  constexpr size_t PER_WARP = (size_t)DQ * ND * 32 + (size_t)DQ * ND * 8 + 2 * DQ * 8 + NDG * DIM * 8;
   extern __shared__ __align__(16) unsigned char smem_raw[];
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   unsigned char *wbase = smem_raw + warp * PER_WARP;
   double4 *stage = reinterpret_cast<double4 *>(wbase);
   double *dnq = reinterpret_cast<double *>(wbase + (size_t)DQ * ND * 32);
   double *facq = dnq + DQ * ND;
-  double *gc = facq + DQ;
+  double *hq = facq + DQ;                                               // mesh_size at the staged points
+  double *gc = hq + DQ;
 
   int ei[T], ej[T];
 #pragma unroll
@@ -174,7 +176,7 @@ __global__ void __launch_bounds__(DW * 32) k_elmat_def(DefArgs A, int64_t count)
     for (int t = 0; t < T; t++) acc[t] = 0.0;
     int np_used = 0;
     if (cut || dom == A.dt) {
-      double cm = A.form.c[0], cs = A.form.c[1], cn = A.form.c[2], cd = A.form.c[3];
+      const double cm0 = A.form.c[0], cs0 = A.form.c[1], cn0 = A.form.c[2], cd0 = A.form.c[3];
       double r2 = 0.0;
 #pragma unroll
       for (int kk = 0; kk < DIM; kk++) { double v = ls[kk] - ls[DIM]; r2 += v * v; }
@@ -184,7 +186,6 @@ __global__ void __launch_bounds__(DW * 32) k_elmat_def(DefArgs A, int64_t count)
       const double4 *rule = iface ? A.rule_if : A.rule_vol;
       const int nr = iface ? A.nr_if : A.nr_vol;
       np_used = E.ns * nr;
-      bool first = true;
       for (int s = 0; s < E.ns; s++) {
         double P[4][3];
         double sfac = 1.0;
@@ -230,18 +231,16 @@ __global__ void __launch_bounds__(DW * 32) k_elmat_def(DefArgs A, int64_t count)
               dnq[lane * ND + i] = dn;
             }
             facq[lane] = adet * (r.w * sfac * scale);
-          }
-          if (first) {
-            first = false;
-            if (hp) {                                                   // mesh_size at the first rule point of the element
-              const double d0 = __shfl_sync(0xffffffffu, adet, 0);
-              const double h = DIM == 2 ? sqrt(d0) : cbrt(d0);
-              cm *= ipow(h, A.form.p[0]); cs *= ipow(h, A.form.p[1]); cn *= ipow(h, A.form.p[2]); cd *= ipow(h, A.form.p[3]);
-            }
+            if (hp) hq[lane] = DIM == 2 ? sqrt(adet) : cbrt(adet);     // mesh_size at this point
           }
           __syncwarp();
           for (int q = 0; q < nq; q++) {
             const double f = facq[q];
+            double cm = cm0, cs = cs0, cn = cn0, cd = cd0;
+            if (hp) {
+              const double h = hq[q];
+              cm *= ipow(h, A.form.p[0]); cs *= ipow(h, A.form.p[1]); cn *= ipow(h, A.form.p[2]); cd *= ipow(h, A.form.p[3]);
+            }
 #pragma unroll
             for (int t = 0; t < T; t++) {
               const double4 bi = stage[q * ND + ei[t]], bj = stage[q * ND + ej[t]];
@@ -418,7 +417,6 @@ __global__ void __launch_bounds__(TT) k_elmat_def_t(DefArgs A, int64_t count) {
     double acc[NT];
 #pragma unroll
     for (int t = 0; t < NT; t++) acc[t] = 0.0;
-    double cm = A.form.c[0], cs = A.form.c[1], cn = A.form.c[2], cd = A.form.c[3];
     double r2 = 0.0;
 #pragma unroll
     for (int a = 0; a < DIM; a++) { double d = ls[a] - ls[DIM]; r2 += d * d; }
@@ -427,7 +425,6 @@ __global__ void __launch_bounds__(TT) k_elmat_def_t(DefArgs A, int64_t count) {
     if (CUTPASS) E = A.tab->e[DIM - 2][A.dt][mask]; else { E.ns = 1; E.npt = 0; }
     const double4 *rule = iface ? srule_if : srule_vol;
     const int nr = iface ? A.nr_if : A.nr_vol;
-    bool first = true;
     for (int s = 0; s < E.ns; s++) {
       double P[4][3];
       double sfac = 1.0;
@@ -447,12 +444,10 @@ __global__ void __launch_bounds__(TT) k_elmat_def_t(DefArgs A, int64_t count) {
         double x[DIM], gl[DIM + 1][DIM], det;
         iso_point<DIM, DORD>(GcThread<TT>{gcs}, lam, x, gl, det);
         const double adet = fabs(det);
-        if (first) {
-          first = false;
-          if (hp) {                                                     // mesh_size at the first rule point of the element
-            const double h = DIM == 2 ? sqrt(adet) : cbrt(adet);
-            cm *= ipow(h, A.form.p[0]); cs *= ipow(h, A.form.p[1]); cn *= ipow(h, A.form.p[2]); cd *= ipow(h, A.form.p[3]);
-          }
+        double cm = A.form.c[0], cs = A.form.c[1], cn = A.form.c[2], cd = A.form.c[3];
+        if (hp) {                                                       // mesh_size at this point (not elementwise constant)
+          const double h = DIM == 2 ? sqrt(adet) : cbrt(adet);
+          cm *= ipow(h, A.form.p[0]); cs *= ipow(h, A.form.p[1]); cn *= ipow(h, A.form.p[2]); cd *= ipow(h, A.form.p[3]);
         }
         double nrm[DIM], g2 = 0.0;
 #pragma unroll
@@ -751,7 +746,7 @@ template <int DIM, int ORDER, int DORD>
 static int launch_elmat_def(DefArgs &A, int sm_count, int64_t nlist, cudaStream_t st) {
   constexpr int ND = H1<DIM, ORDER>::ND, NDG = H1<DIM, DORD>::ND;
   if (g_def_warp) {
-    const size_t smem = DW * ((size_t)DQ * ND * 32 + (size_t)DQ * ND * 8 + DQ * 8 + NDG * DIM * 8);
+    const size_t smem = DW * ((size_t)DQ * ND * 32 + (size_t)DQ * ND * 8 + 2 * DQ * 8 + NDG * DIM * 8);
     auto kern = k_elmat_def<DIM, ORDER, DORD>;
     unsigned grid;
     if (int rc = grid_for(kern, smem, sm_count, nlist, &grid)) return rc;

@@ -25,9 +25,18 @@ PYSP="$(python3 -c 'import site;print(site.getsitepackages()[0])')"
 OB="$PYSP/opencv_python_headless.libs"
 OBLIB="$(ls "$OB"/libopenblasp-r0-*.so 2>/dev/null | head -1 || true)"
 
+# MapPatchIntegrationPoint<D> (xfem/symboliccutbfi.cpp): the one template of that file the driver calls.  The file as a whole
+# needs NGSolve's comp layer + SymbolicBilinearFormIntegrator (do not link here), so the template is lifted out at build time
+# into the git-ignored output directory -- from "template<int D>" before "void MapPatchIntegrationPoint(" to its closing brace.
+awk '/^  template<int D>$/ { held = $0; next }
+     held != "" { if ($0 ~ /void MapPatchIntegrationPoint\(/) { print held; on = 1 } held = "" }
+     on { print }
+     on && /^  }$/ { exit }' "$REF/xfem/symboliccutbfi.cpp" > "$OUT/mappatch_extract.hpp"
+grep -q "MapPatchIntegrationPoint" "$OUT/mappatch_extract.hpp" || { echo "build_ref.sh: could not extract MapPatchIntegrationPoint"; exit 1; }
+
 INC="-I$OUT -I$NGS/include -I$NGS/ngstd -I$NGS/basiclinalg -I$NGS/fem -I$NGS/comp -I$NGS/linalg -I$NGS/solve \
  -I$NGS/multigrid -I$NGS/parallel -I$NG/libsrc/include -I$NG/libsrc -I$NG/libsrc/core -I$NG/libsrc/visualization \
- -I$REF/cutint -I$REF/utils -I$REF -DELEMENT_MAXPOINTS=20"
+ -I$REF/cutint -I$REF/utils -I$REF/xfem -I$REF -DELEMENT_MAXPOINTS=20"
 CXX="g++ -std=c++17 -O2 -fPIC -w -Wno-psabi -fopenmp"
 
 # netgen's version.hpp wants a generated netgen_version.hpp
@@ -83,14 +92,17 @@ done
 BLA_OBJS+=("$OBJ/bla_ngblas.o"); par compile "$NGS/basiclinalg/ngblas.cpp" "$OBJ/bla_ngblas.o" -DLAPACK
 FEM_OBJS=()
 for b in recursive_pol elementtopology finiteelement scalarfe intrule elementtransformation h1lofe h1hofe h1hofe_trig h1hofe_segm \
-         l2hofe l2hofe_segm l2hofe_trig l2hofe_tet; do
+         l2hofe l2hofe_segm l2hofe_trig l2hofe_tet diffop integrator; do
   FEM_OBJS+=("$OBJ/fem_$b.o"); par compile "$NGS/fem/$b.cpp" "$OBJ/fem_$b.o"
 done
-X_OBJS=("$OBJ/x_xdecompose.o" "$OBJ/x_straightcutrule.o" "$OBJ/x_SpaceTimeFE.o" "$OBJ/x_spacetimecutrule.o")
+X_OBJS=("$OBJ/x_xdecompose.o" "$OBJ/x_straightcutrule.o" "$OBJ/x_SpaceTimeFE.o" "$OBJ/x_spacetimecutrule.o" "$OBJ/x_xfiniteelement.o" "$OBJ/x_xfemdiffops.o")
+par compile "$REF/xfem/xfiniteelement.cpp" "$OBJ/x_xfiniteelement.o"
+par compile "$REF/xfem/xfemdiffops.cpp" "$OBJ/x_xfemdiffops.o"
 par compile "$REF/spacetime/SpaceTimeFE.cpp" "$OBJ/x_SpaceTimeFE.o"
 par compile "$REF/cutint/spacetimecutrule.cpp" "$OBJ/x_spacetimecutrule.o"
 par compile "$REF/cutint/xdecompose.cpp" "$OBJ/x_xdecompose.o"
 par compile "$REF/cutint/straightcutrule.cpp" "$OBJ/x_straightcutrule.o"
+if [ "$OUT/mappatch_extract.hpp" -nt "$OBJ/ref_driver.o" ]; then rm -f "$OBJ/ref_driver.o"; fi
 par compile "$HERE/ref_driver.cpp" "$OBJ/ref_driver.o"
 waitall
 

@@ -587,7 +587,9 @@ int orc_cut_rule_iso(int dim, int dord, const double *gcoef, const double *ls, i
 /* xfem/symboliccutbfi.cpp:73-315 on a deformed element.  form[8] = {c_mass, c_stiff, c_nitsche, c_dndn, hpow_mass, hpow_stiff,
  * hpow_nitsche, hpow_dndn}: c_m u v + c_s grad u.grad v + c_n ((grad u.n) v + (grad v.n) u) + c_d (grad u.n)(grad v.n),
  * n = grad(lset)/|grad(lset)| evaluated per point on the deformed element (a GridFunction CF), h = specialcf.mesh_size =
- * |det F|^(1/dim): flagged ElementwiseConstant, so the reference evaluates it at the FIRST point of the rule only (:205-214). */
+ * |det F|^(1/dim) (NGS/fem/python_fem.cpp:564-593) evaluated PER POINT: MeshSizeCF is not flagged ElementwiseConstant
+ * (NGS/fem/coefficient.hpp:22 default false; products inherit c1 && c2, NGS/fem/coefficient.cpp:1349), so the reference takes
+ * the cf->Evaluate(mir, val) branch of :205-214.  Pinned against ref_elmat_h1_form (oracle/ref_driver.cpp). */
 int orc_elmat_h1_iso(int dim, int fe_order, int dord, const double *gcoef, const double *ls, int dt, int intorder,
                      const double *form, double *elmat)
 {
@@ -596,18 +598,18 @@ int orc_elmat_h1_iso(int dim, int fe_order, int dord, const double *gcoef, const
   int nd = orc_h1_ndof(dim, fe_order);
   if (np < 0) return np;
   for (int i = 0; i < nd*nd; i++) elmat[i] = 0;
-  double c[4] = {form[0], form[1], form[2], form[3]};
-  if (np > 0) {
-    double h = pow(meas[0], 1.0 / dim);
-    for (int t = 0; t < 4; t++) {
-      int p = (int)form[4 + t];
-      double f = 1.0, b = p < 0 ? 1.0 / h : h;
-      for (int k = 0; k < abs(p); k++) f *= b;
-      c[t] *= f;
-    }
-  }
   double shape[ORC_MAXND], dref[ORC_MAXND*3], dphys[ORC_MAXND*3], dn[ORC_MAXND];
   for (int q = 0; q < np; q++) {
+    double c[4] = {form[0], form[1], form[2], form[3]};
+    {
+      double h = pow(meas[q], 1.0 / dim);
+      for (int t = 0; t < 4; t++) {
+        int p = (int)form[4 + t];
+        double f = 1.0, b = p < 0 ? 1.0 / h : h;
+        for (int k = 0; k < abs(p); k++) f *= b;
+        c[t] *= f;
+      }
+    }
     double x[3], J[3][3], Ji[3][3], det, n[3] = {0, 0, 0};
     iso_eval(dim, dord, gcoef, pts + 3*q, x, J, Ji, &det);
     if (orc_h1_shape(dim, fe_order, 0, pts + 3*q, shape, dref) < 0) return ORC_UNSUP;

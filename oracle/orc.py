@@ -205,11 +205,32 @@ def elvec_h1(dim, fe_order, vnums, pmat, lset, dt, intorder, mono, impl="oracle"
     return n, ev
 
 
-def facetpatch_elmat_h1(dim, fe_order, vn1, pmat1, vn2, pmat2, coef, hpow=0):
+def facetpatch_elmat_h1(dim, fe_order, vn1, pmat1, vn2, pmat2, coef, hpow=0, impl="oracle", dord=0):
+    """impl="ref": the compiled reference (MapPatchIntegrationPoint of xfem/symboliccutbfi.cpp + H1HighOrderFE); dord >= 1:
+    pmat1 / pmat2 are the coefficients of the isoparametric geometry elements (deformed mesh)"""
     nd = load().orc_h1_ndof(dim, fe_order)
     em = np.zeros((2 * nd, 2 * nd))
     a, b, p1, p2 = _i(vn1), _i(vn2), _d(pmat1), _d(pmat2)
-    n = load().orc_facetpatch_elmat_h1(dim, fe_order, P(a, ip), P(p1), P(b, ip), P(p2), coef, hpow, P(em))
+    if impl == "oracle":
+        if dord == 0:
+            n = load().orc_facetpatch_elmat_h1(dim, fe_order, P(a, ip), P(p1), P(b, ip), P(p2), coef, hpow, P(em))
+        else:
+            n = load().orc_facetpatch_elmat_h1_iso(dim, fe_order, dord, P(a, ip), P(p1), P(b, ip), P(p2), coef, hpow, P(em))
+    else:
+        from . import refload
+        n = refload.load().ref_facetpatch_elmat_h1(ET[dim], fe_order, dord, P(a, ip), P(p1), P(b, ip), P(p2), coef, hpow, P(em), None)
+    return n, em
+
+
+def elmat_h1_form(dim, fe_order, vnums, geom, lset, dt, intorder, form, dord=0):
+    """compiled reference only: general ngsx_form_h1 element matrix (Nitsche / dn.dn terms, mesh_size powers), affine (dord 0:
+    geom = vertex matrix) or isoparametric (geom = geometry coefficients)"""
+    from . import refload
+    nd = load().orc_h1_ndof(dim, fe_order)
+    em = np.zeros((nd, nd))
+    vn = _i(vnums) if vnums is not None else None
+    g = _d(geom); ls = _d(lset); f = _d(form)
+    n = refload.load().ref_elmat_h1_form(ET[dim], fe_order, dord, P(vn, ip) if vn is not None else None, P(g), P(ls), dt, intorder, P(f), P(em))
     return n, em
 
 

@@ -10,19 +10,34 @@
 //   * ngfem::FE_ElementTransformation / MappedIntegrationRule   (NGS/fem/elementtransformation.cpp)
 //   * xintegration::SpaceTimeCutIntegrationRule + ngfem::NodalTimeFE (cutint/spacetimecutrule.cpp:98-196, spacetime/SpaceTimeFE.cpp:116-173)
 //   * ngbla::AddABt                                             (NGS/basiclinalg/ngblas.cpp)
+//   * ngfem::T_DifferentialOperator<DiffOpX<D, RNEG/RPOS/RNEG_GRAD/RPOS_GRAD>>::CalcMatrix on ngfem::XFiniteElement
+//                                                               (xfem/xfemdiffops.cpp:8-82, xfem/xfiniteelement.cpp:12-31)
+//   * MapPatchIntegrationPoint<D>                               (xfem/symboliccutbfi.cpp:1113-1199; the template is lifted out
+//     of the reference file at build time by oracle/build_ref.sh into the git-ignored oracle/_ref/mappatch_extract.hpp:
+//     the rest of that file needs NGSolve's comp layer and SymbolicBilinearFormIntegrator, which do not link here)
 // The only restated logic is the ~30-line B*D*B^T accumulation of
-// xfem/symboliccutbfi.cpp:219-301 (diagonal-proxy branch; the symbolic
+// xfem/symboliccutbfi.cpp:219-301 and :1337-1408 (the symbolic
 // CoefficientFunction tree of the reference cannot be built without the full
-// NGSolve comp layer) and the CutInformation::Update decision of
-// xfem/cutinfo.cpp:79-111.
+// NGSolve comp layer; the coefficient functions of the tutorials' forms --
+// constants, specialcf.mesh_size = |det F|^(1/D) per point (NGS/fem/python_fem.cpp:564-593), the level-set normal
+// grad(lsetp1)/|grad(lsetp1)|, CutRatioGF -- are evaluated from the reference's own mapped points and shapes) and the
+// CutInformation::Update decision of xfem/cutinfo.cpp:79-111.
 #include <fem.hpp>
 #include "../cutint/straightcutrule.hpp"
 #include "../cutint/spacetimecutrule.hpp"
 #include "../spacetime/SpaceTimeFE.hpp"
+#include "../xfem/xfiniteelement.hpp"
+#include "../xfem/xfemdiffops.hpp"
 #include <omp.h>
 
 using namespace ngfem;
 using namespace xintegration;
+
+namespace refpatch {
+  using namespace std;
+  using namespace ngfem;
+#include "mappatch_extract.hpp"
+}
 
 namespace {
 
@@ -269,6 +284,275 @@ struct ElmatWork
     return np;
   }
 };
+
+// element transformation of one element: dord == 0: affine from the vertex matrix geom [(D+1)][D]; dord >= 1: isoparametric,
+// geom = coefficients of the H1HighOrderFE<ET>(dord) geometry element (IsoTrafo above)
+template <ELEMENT_TYPE ET>
+FE_ElementTransformation<ET_trait<ET>::DIM, ET_trait<ET>::DIM> * MakeTrafo(int dord, const double * geom, LocalHeap & lh)
+{
+  constexpr int D = ET_trait<ET>::DIM;
+  if (dord >= 1) return IsoTrafo<ET>(dord, geom, lh);
+  Matrix<> pm(D+1, D);
+  for (int i = 0; i < D+1; i++) for (int d = 0; d < D; d++) pm(i,d) = geom[i*D+d];
+  return new (lh) FE_ElementTransformation<D,D>(ET, pm);
+}
+
+// specialcf.mesh_size (NGS/fem/python_fem.cpp:564-593, volume point): |det F|^(1/D)
+template <int D> double MeshSize(const MappedIntegrationPoint<D,D> & mip)
+{
+  double det = fabs(mip.GetJacobiDet());
+  return D == 1 ? det : pow(det, 1.0/D);
+}
+
+// n = grad(lsetp1)/|grad(lsetp1)| at a mapped point: the gradient of the P1 GridFunction through the reference's own
+// H1HighOrderFE(1)::CalcMappedDShape (what grad(gf) evaluates, NGS/comp/gridfunction.cpp via DiffOpGradient)
+template <ELEMENT_TYPE ET>
+Vec<ET_trait<ET>::DIM> LsetNormal(const MappedIntegrationPoint<ET_trait<ET>::DIM, ET_trait<ET>::DIM> & mip, const double * lset, LocalHeap & lh)
+{
+  constexpr int D = ET_trait<ET>::DIM;
+  HeapReset hr(lh);
+  H1HighOrderFE<ET> p1(1);
+  FlatMatrixFixWidth<D> ds(D+1, lh);
+  p1.CalcMappedDShape(mip, ds);
+  Vec<D> g = 0.0;
+  for (int i = 0; i < D+1; i++) for (int d = 0; d < D; d++) g(d) += lset[i] * ds(i,d);
+  g /= L2Norm(g);
+  return g;
+}
+
+// SymbolicCutBFI with the forms of py_tutorials/fictdom_ghostpen.py:86-96 / tracefem3d.py:74-88 on one element:
+//   c_s h^ps grad u.grad v + c_m h^pm u v + c_n h^pn ((grad u.n) v + (grad v.n) u) + c_d h^pd (grad u.n)(grad v.n)
+// form8 = {c_mass, c_stiff, c_nitsche, c_dndn, hpow_mass, hpow_stiff, hpow_nitsche, hpow_dndn}.  Rule, mapped points, measure,
+// shapes and mapped gradients are the reference's; mesh_size and the normal are evaluated PER POINT (a coefficient tree that
+// contains them is not elementwise constant, NGS/fem/coefficient.cpp:1349, xfem/symboliccutbfi.cpp:205-214).
+template <ELEMENT_TYPE ET>
+int ElmatForm(int fe_order, int dord, const int * vnums, const double * geom, const double * lset, int dt, int intorder,
+              const double * form8, double * elmat_out, LocalHeap & lh)
+{
+  constexpr int D = ET_trait<ET>::DIM;
+  H1HighOrderFE<ET> fel(fe_order);
+  if (vnums) for (int i = 0; i < D+1; i++) fel.SetVertexNumber(i, vnums[i]);
+  int nd = fel.GetNDof();
+  auto trafo = MakeTrafo<ET>(dord, geom, lh);
+  Vector<> lv(D+1);
+  for (int i = 0; i < D+1; i++) lv(i) = lset[i];
+  const IntegrationRule * ir = StraightCutIntegrationRule(lv, *trafo, DOMAIN_TYPE(dt), intorder, FIND_OPTIMAL, lh);
+  if (!ir) return -1;
+  int np = ir->Size();
+  MappedIntegrationRule<D,D> mir(*ir, *trafo, lh);
+  FlatMatrix<> elmat(nd, nd, lh); elmat = 0.0;
+  FlatVector<> shape(nd, lh), dn(nd, lh);
+  FlatMatrixFixWidth<D> dshape(nd, lh);
+  for (int q = 0; q < np; q++)
+    {
+      double fac = mir[q].GetMeasure() * (*ir)[q].Weight();
+      double h = MeshSize<D>(mir[q]);
+      fel.CalcShape((*ir)[q], shape);
+      fel.CalcMappedDShape(mir[q], dshape);
+      Vec<D> n = LsetNormal<ET>(mir[q], lset, lh);
+      dn = dshape * n;
+      double cm = form8[0] * pow(h, form8[4]) * fac, cs = form8[1] * pow(h, form8[5]) * fac;
+      double cn = form8[2] * pow(h, form8[6]) * fac, cd = form8[3] * pow(h, form8[7]) * fac;
+      for (int i = 0; i < nd; i++) for (int j = 0; j < nd; j++)
+        {
+          double gg = 0; for (int d = 0; d < D; d++) gg += dshape(i,d) * dshape(j,d);
+          elmat(i,j) += cs * gg + cm * shape(i) * shape(j) + cn * (dn(j) * shape(i) + dn(i) * shape(j)) + cd * dn(i) * dn(j);
+        }
+    }
+  for (int i = 0; i < nd; i++) for (int j = 0; j < nd; j++) elmat_out[i*nd+j] = elmat(i,j);
+  return np;
+}
+
+// SymbolicFacetPatchBilinearFormIntegrator::CalcFacetMatrix (xfem/symboliccutbfi.cpp:1202-1411, time_order == -1) for the
+// ghost-penalty form coef * h^hpow * (u - u.Other()) * (v - v.Other()) (py_tutorials/fictdom_ghostpen.py:105-107):
+// volume rules of order 2*maxorder on both elements (:1219-1220), every point pulled into the other element by the
+// reference's MapPatchIntegrationPoint (:1229-1244), weights mir1.GetWeight() (:1365), the coefficient evaluated on mir1 (:1359).
+// elmat (2 nd)x(2 nd) row-major over [dofs of element 1 | dofs of element 2].  Returns the number of patch points.
+template <ELEMENT_TYPE ET>
+int FacetPatch(int fe_order, int dord, const int * vn1, const double * g1, const int * vn2, const double * g2,
+               double coef, int hpow, double * elmat_out, double * ip2_out, LocalHeap & lh)
+{
+  constexpr int D = ET_trait<ET>::DIM;
+  H1HighOrderFE<ET> fel1(fe_order), fel2(fe_order);
+  for (int i = 0; i < D+1; i++) { if (vn1) fel1.SetVertexNumber(i, vn1[i]); if (vn2) fel2.SetVertexNumber(i, vn2[i]); }
+  int nd = fel1.GetNDof(), n2 = 2*nd;
+  auto trafo1 = MakeTrafo<ET>(dord, g1, lh);
+  auto trafo2 = MakeTrafo<ET>(dord, g2, lh);
+  IntegrationRule ir_vol1(ET, 2*fe_order);
+  IntegrationRule ir_vol2(ET, 2*fe_order);
+  IntegrationRule ir_patch1 (ir_vol1.Size()+ir_vol2.Size(),lh);
+  IntegrationRule ir_patch2 (ir_vol1.Size()+ir_vol2.Size(),lh);
+  for (int l = 0; l < ir_patch1.Size(); l++)
+    {
+      if (l < ir_vol1.Size())
+        {
+          ir_patch1[l] = ir_vol1[l];
+          refpatch::MapPatchIntegrationPoint<D>(ir_patch1[l], *trafo1, *trafo2, ir_patch2[l], lh);
+        }
+      else
+        {
+          ir_patch2[l] = ir_vol2[l - ir_vol1.Size()];
+          refpatch::MapPatchIntegrationPoint<D>(ir_patch2[l], *trafo2, *trafo1, ir_patch1[l], lh);
+        }
+    }
+  MappedIntegrationRule<D,D> mir1(ir_patch1, *trafo1, lh);
+  FlatMatrix<> elmat(n2, n2, lh); elmat = 0.0;
+  FlatVector<> sh1(nd, lh), sh2(nd, lh), jump(n2, lh);
+  for (int i = 0; i < mir1.Size(); i++)
+    {
+      double val = coef * pow(MeshSize<D>(mir1[i]), hpow) * mir1[i].GetWeight();
+      fel1.CalcShape(ir_patch1[i], sh1);
+      fel2.CalcShape(ir_patch2[i], sh2);
+      jump.Range(0, nd) = sh1;
+      jump.Range(nd, n2) = -sh2;
+      elmat += val * jump * Trans(jump);
+      if (ip2_out) for (int d = 0; d < 3; d++) { ip2_out[6*i+d] = ir_patch1[i](d); ip2_out[6*i+3+d] = ir_patch2[i](d); }
+    }
+  for (int i = 0; i < n2; i++) for (int j = 0; j < n2; j++) elmat_out[i*n2+j] = elmat(i,j);
+  return mir1.Size();
+}
+
+// B-vectors of the compound element [H1 element | XFiniteElement] at one mapped point: values U[k] and mapped gradients G[k]
+// of u_std + op_k(u_x), k = NEG, POS -- the x-part through the reference's DiffOpX (xfem/xfemdiffops.cpp:8-82)
+template <ELEMENT_TYPE ET>
+struct XB
+{
+  enum { D = ET_trait<ET>::DIM };
+  T_DifferentialOperator<DiffOpX<D,DIFFOPX::RNEG>> rneg;
+  T_DifferentialOperator<DiffOpX<D,DIFFOPX::RPOS>> rpos;
+  T_DifferentialOperator<DiffOpX<D,DIFFOPX::RNEG_GRAD>> rneg_grad;
+  T_DifferentialOperator<DiffOpX<D,DIFFOPX::RPOS_GRAD>> rpos_grad;
+
+  void Eval(const H1HighOrderFE<ET> & fel, const XFiniteElement & xfe, const MappedIntegrationPoint<D,D> & mip,
+            FlatMatrix<> U /* 2 x 2nd */, FlatMatrix<> G /* 2*D x 2nd */, LocalHeap & lh) const
+  {
+    HeapReset hr(lh);
+    int nd = fel.GetNDof();
+    FlatVector<> shape(nd, lh);
+    FlatMatrixFixWidth<D> dshape(nd, lh);
+    fel.CalcShape(mip.IP(), shape);
+    fel.CalcMappedDShape(mip, dshape);
+    FlatMatrix<double,ColMajor> bv(1, nd, lh), bg(D, nd, lh);
+    for (int k = 0; k < 2; k++)
+      {
+        const DifferentialOperator & ov = k == 0 ? (const DifferentialOperator&)rneg : (const DifferentialOperator&)rpos;
+        const DifferentialOperator & og = k == 0 ? (const DifferentialOperator&)rneg_grad : (const DifferentialOperator&)rpos_grad;
+        ov.CalcMatrix(xfe, mip, bv, lh);
+        og.CalcMatrix(xfe, mip, bg, lh);
+        for (int i = 0; i < nd; i++)
+          {
+            U(k, i) = shape(i); U(k, nd+i) = bv(0, i);
+            for (int d = 0; d < D; d++) { G(k*D+d, i) = dshape(i,d); G(k*D+d, nd+i) = bg(d, i); }
+          }
+      }
+  }
+};
+
+// two-phase Nitsche-XFEM element matrix of py_tutorials/nxfem.py:77-107 on the compound element (the three integrators
+// summed): NEG alpha0 gradu0.gradv0 (order 2p-2), POS alpha1 gradu1.gradv1, IF avgflux_u [v] + avgflux_v [u] + stab [u][v]
+// (order 2p), stab = stab_factor (alpha0+alpha1)/h, avgflux = -sum_k kappa_k alpha_k grad u_k . n, kappa = (ratio, 1-ratio).
+// xsign == nullptr: uncut element (no x-dofs): the nd x nd block of the std dofs.  elmat (2nd)x(2nd) (or nd x nd) row-major.
+template <ELEMENT_TYPE ET>
+int NxfemElmat(int fe_order, const int * vnums, const double * pmat, const double * lset, const signed char * xsign,
+               double kappa_neg, double alpha0, double alpha1, double stab_factor, double * elmat_out, LocalHeap & lh)
+{
+  constexpr int D = ET_trait<ET>::DIM;
+  H1HighOrderFE<ET> fel(fe_order);
+  if (vnums) for (int i = 0; i < D+1; i++) fel.SetVertexNumber(i, vnums[i]);
+  int nd = fel.GetNDof(), n2 = 2*nd;
+  Array<DOMAIN_TYPE> signs(nd);
+  for (int i = 0; i < nd; i++) signs[i] = xsign ? DOMAIN_TYPE(xsign[i]) : IF;      // IF matches neither RNEG nor RPOS: zero x-part
+  XFiniteElement xfe(fel, signs, lh);
+  XB<ET> xb;
+  auto trafo = MakeTrafo<ET>(0, pmat, lh);
+  Vector<> lv(D+1);
+  for (int i = 0; i < D+1; i++) lv(i) = lset[i];
+  FlatMatrix<> A(n2, n2, lh); A = 0.0;
+  FlatMatrix<> U(2, n2, lh), G(2*D, n2, lh);
+  double alpha[2] = {alpha0, alpha1}, kappa[2] = {kappa_neg, 1.0 - kappa_neg};
+  int total = 0;
+  for (int dt = 0; dt < 2; dt++)
+    {
+      const IntegrationRule * ir = StraightCutIntegrationRule(lv, *trafo, DOMAIN_TYPE(dt), 2*fe_order-2, FIND_OPTIMAL, lh);
+      if (!ir) continue;
+      MappedIntegrationRule<D,D> mir(*ir, *trafo, lh);
+      total += ir->Size();
+      for (int q = 0; q < ir->Size(); q++)
+        {
+          xb.Eval(fel, xfe, mir[q], U, G, lh);
+          double fac = mir[q].GetMeasure() * (*ir)[q].Weight() * alpha[dt];
+          for (int i = 0; i < n2; i++) for (int j = 0; j < n2; j++)
+            for (int d = 0; d < D; d++) A(i,j) += fac * G(dt*D+d, i) * G(dt*D+d, j);
+        }
+    }
+  const IntegrationRule * ir = StraightCutIntegrationRule(lv, *trafo, IF, 2*fe_order, FIND_OPTIMAL, lh);
+  if (ir)
+    {
+      MappedIntegrationRule<D,D> mir(*ir, *trafo, lh);
+      total += ir->Size();
+      FlatVector<> flux(n2, lh), jump(n2, lh);
+      for (int q = 0; q < ir->Size(); q++)
+        {
+          xb.Eval(fel, xfe, mir[q], U, G, lh);
+          Vec<D> n = LsetNormal<ET>(mir[q], lset, lh);
+          double stab = stab_factor * (alpha0 + alpha1) / MeshSize<D>(mir[q]);
+          for (int i = 0; i < n2; i++)
+            {
+              double f = 0;
+              for (int k = 0; k < 2; k++) for (int d = 0; d < D; d++) f -= kappa[k] * alpha[k] * G(k*D+d, i) * n(d);
+              flux(i) = f;
+              jump(i) = U(0,i) - U(1,i);
+            }
+          double fac = mir[q].GetMeasure() * (*ir)[q].Weight();
+          for (int i = 0; i < n2; i++) for (int j = 0; j < n2; j++)
+            A(i,j) += fac * (jump(i)*flux(j) + flux(i)*jump(j) + stab * jump(i)*jump(j));
+        }
+    }
+  int no = xsign ? n2 : nd;
+  for (int i = 0; i < no; i++) for (int j = 0; j < no; j++) elmat_out[i*no+j] = A(i,j);
+  return total;
+}
+
+// SymbolicLFI(levelset_domain = dt, form = f (v_std + op(v_x))), op = neg (dt NEG) / pos (dt POS), py_tutorials/nxfem.py:109-110
+template <ELEMENT_TYPE ET>
+int NxfemElvec(int fe_order, const int * vnums, const double * pmat, const double * lset, const signed char * xsign, int dt,
+               int nmono, const double * mono, double * elvec_out, LocalHeap & lh)
+{
+  constexpr int D = ET_trait<ET>::DIM;
+  H1HighOrderFE<ET> fel(fe_order);
+  if (vnums) for (int i = 0; i < D+1; i++) fel.SetVertexNumber(i, vnums[i]);
+  int nd = fel.GetNDof(), n2 = 2*nd;
+  Array<DOMAIN_TYPE> signs(nd);
+  for (int i = 0; i < nd; i++) signs[i] = xsign ? DOMAIN_TYPE(xsign[i]) : IF;
+  XFiniteElement xfe(fel, signs, lh);
+  XB<ET> xb;
+  auto trafo = MakeTrafo<ET>(0, pmat, lh);
+  Vector<> lv(D+1);
+  for (int i = 0; i < D+1; i++) lv(i) = lset[i];
+  const IntegrationRule * ir = StraightCutIntegrationRule(lv, *trafo, DOMAIN_TYPE(dt), 2*fe_order, FIND_OPTIMAL, lh);
+  FlatVector<> b(n2, lh); b = 0.0;
+  int np = -1;
+  if (ir)
+    {
+      np = ir->Size();
+      MappedIntegrationRule<D,D> mir(*ir, *trafo, lh);
+      FlatMatrix<> U(2, n2, lh), G(2*D, n2, lh);
+      for (int q = 0; q < np; q++)
+        {
+          xb.Eval(fel, xfe, mir[q], U, G, lh);
+          double x[3] = {0,0,0};
+          for (int d = 0; d < D; d++) x[d] = mir[q].GetPoint()(d);
+          double f = 0;
+          for (int m = 0; m < nmono; m++)
+            f += mono[4*m] * pow(x[0], mono[4*m+1]) * pow(x[1], mono[4*m+2]) * pow(x[2], mono[4*m+3]);
+          double fac = mir[q].GetMeasure() * (*ir)[q].Weight() * f;
+          for (int i = 0; i < n2; i++) b(i) += fac * U(dt, i);
+        }
+    }
+  int no = xsign ? n2 : nd;
+  for (int i = 0; i < no; i++) elvec_out[i] = b(i);
+  return np;
+}
 
 } // namespace
 
@@ -586,6 +870,53 @@ long ref_assemble_csr(int dim, const int * el2v, const double * vert, const doub
         }
     }
   return nass;
+}
+
+// general ngsx_form_h1 element matrix (Nitsche / normal-normal terms, powers of mesh_size) on an affine (dord = 0) or
+// isoparametric element
+int ref_elmat_h1_form(int et, int fe_order, int dord, const int * vnums, const double * geom, const double * lset, int dt, int intorder,
+                      const double * form8, double * elmat)
+{
+  LocalHeap & lh = GetLH(); HeapReset hr(lh);
+  try {
+    if (et == ET_TRIG) return ElmatForm<ET_TRIG>(fe_order, dord, vnums, geom, lset, dt, intorder, form8, elmat, lh);
+    if (et == ET_TET) return ElmatForm<ET_TET>(fe_order, dord, vnums, geom, lset, dt, intorder, form8, elmat, lh);
+    return -4;
+  } catch (...) { return -2; }
+}
+
+// facet-patch (ghost penalty) matrix; ip2 (may be NULL) [npts][6]: the patch points in the reference coordinates of both elements
+int ref_facetpatch_elmat_h1(int et, int fe_order, int dord, const int * vn1, const double * g1, const int * vn2, const double * g2,
+                            double coef, int hpow, double * elmat, double * ip2)
+{
+  LocalHeap & lh = GetLH(); HeapReset hr(lh);
+  try {
+    if (et == ET_TRIG) return FacetPatch<ET_TRIG>(fe_order, dord, vn1, g1, vn2, g2, coef, hpow, elmat, ip2, lh);
+    if (et == ET_TET) return FacetPatch<ET_TET>(fe_order, dord, vn1, g1, vn2, g2, coef, hpow, elmat, ip2, lh);
+    return -4;
+  } catch (...) { return -2; }
+}
+
+int ref_nxfem_elmat(int et, int fe_order, const int * vnums, const double * pmat, const double * lset, const signed char * xsign,
+                    double kappa_neg, double alpha0, double alpha1, double stab_factor, double * elmat)
+{
+  LocalHeap & lh = GetLH(); HeapReset hr(lh);
+  try {
+    if (et == ET_TRIG) return NxfemElmat<ET_TRIG>(fe_order, vnums, pmat, lset, xsign, kappa_neg, alpha0, alpha1, stab_factor, elmat, lh);
+    if (et == ET_TET) return NxfemElmat<ET_TET>(fe_order, vnums, pmat, lset, xsign, kappa_neg, alpha0, alpha1, stab_factor, elmat, lh);
+    return -4;
+  } catch (...) { return -2; }
+}
+
+int ref_nxfem_elvec(int et, int fe_order, const int * vnums, const double * pmat, const double * lset, const signed char * xsign, int dt,
+                    int nmono, const double * mono, double * elvec)
+{
+  LocalHeap & lh = GetLH(); HeapReset hr(lh);
+  try {
+    if (et == ET_TRIG) return NxfemElvec<ET_TRIG>(fe_order, vnums, pmat, lset, xsign, dt, nmono, mono, elvec, lh);
+    if (et == ET_TET) return NxfemElvec<ET_TET>(fe_order, vnums, pmat, lset, xsign, dt, nmono, mono, elvec, lh);
+    return -4;
+  } catch (...) { return -2; }
 }
 
 int ref_max_threads() { return omp_get_max_threads(); }

@@ -96,3 +96,39 @@ def nxfem_elvec(dim, order, vnums, pmat, ls, xsign, dt, fpoly):
         f = sum(c * x[0] ** e[0] * x[1] ** e[1] * x[2] ** e[2] for e, c in fpoly.items())
         b += meas * w[q] * f * np.concatenate([s, m * s])
     return b if xsign is not None else b[:nd]
+
+
+# ---------------------------------------------------------------------------------------------------------------------
+# the same two functions through the reference's own DiffOpX / XFiniteElement (oracle/_ref, ref_driver.cpp:NxfemElmat):
+# what pins the numpy restatement above (tests/test_oracle_vs_ref.py::test_xfem_*)
+# ---------------------------------------------------------------------------------------------------------------------
+def nxfem_elmat_ref(dim, order, vnums, pmat, ls, xsign, kappa_neg, alpha, stab_factor):
+    import ctypes
+    from . import refload
+    L = refload.load()
+    nd = orc.load().orc_h1_ndof(dim, order)
+    n = 2 * nd if xsign is not None else nd
+    em = np.zeros((n, n))
+    vn = np.ascontiguousarray(vnums, dtype=np.int32); pm = np.ascontiguousarray(pmat, dtype=np.float64)
+    l = np.ascontiguousarray(ls, dtype=np.float64)
+    xs = None if xsign is None else np.ascontiguousarray(xsign, dtype=np.int8)
+    xp = None if xs is None else xs.ctypes.data_as(ctypes.POINTER(ctypes.c_byte))
+    r = L.ref_nxfem_elmat(orc.ET[dim], order, orc.P(vn, orc.ip), orc.P(pm), orc.P(l), xp, kappa_neg, alpha[0], alpha[1], stab_factor, orc.P(em))
+    assert r >= 0, r
+    return em
+
+
+def nxfem_elvec_ref(dim, order, vnums, pmat, ls, xsign, dt, fpoly):
+    import ctypes
+    from . import refload
+    L = refload.load()
+    nd = orc.load().orc_h1_ndof(dim, order)
+    n = 2 * nd if xsign is not None else nd
+    ev = np.zeros(n)
+    vn = np.ascontiguousarray(vnums, dtype=np.int32); pm = np.ascontiguousarray(pmat, dtype=np.float64)
+    l = np.ascontiguousarray(ls, dtype=np.float64)
+    xs = None if xsign is None else np.ascontiguousarray(xsign, dtype=np.int8)
+    xp = None if xs is None else xs.ctypes.data_as(ctypes.POINTER(ctypes.c_byte))
+    mono = orc.mono_array([(c, e[0], e[1], e[2]) for e, c in fpoly.items()])
+    L.ref_nxfem_elvec(orc.ET[dim], order, orc.P(vn, orc.ip), orc.P(pm), orc.P(l), xp, dt, len(mono), orc.P(mono), orc.P(ev))
+    return ev

@@ -1246,3 +1246,111 @@ def test_order3_elmats_and_assembly(X, dim, nx):
         c = X.xfem.BilinearForm(V4)
         c += X.xfem.SymbolicBFI(levelset_domain={"levelset": gf, "domain_type": NEG}, form=u * v)
         c.Assemble()
+
+
+# ------------------------------------------------------------------------------------------------------------------
+# round 2: the parity holes the round-1 review listed (a-0 clamp band, node marks, order 3 under vertex permutations)
+# ------------------------------------------------------------------------------------------------------------------
+def test_interpolate_p1_clamp_band(X):
+    """a-0: |v| < eps_perturbation -> +eps (utils/p1interpol.cpp:88-90), bit-exact against the C restatement, on both branches;
+    values inside the band on purpose (signed zeros, denormals, +-eps itself)"""
+    from oracle import orc
+    mesh = X.ngs.Mesh(X.meshes.MakeStructured3DMesh(4))
+    V1 = X.ngs.H1(mesh, order=1)
+    eps = 1e-14
+    band = np.array([1e-15, -1e-15, 0.0, -0.0, eps, -eps, np.nextafter(eps, 0), -np.nextafter(eps, 0), np.nextafter(eps, 1), 5e-324, -5e-324,
+                     1e-13, -1e-13, 0.3, -0.3])
+    rng = np.random.default_rng(5)
+    vals = rng.uniform(-1, 1, mesh.nv) * 10.0 ** rng.integers(-18, 1, mesh.nv)
+    vals[: len(band)] = band
+    src = X.ngs.GridFunction(X.ngs.H1(mesh, order=2))                          # higher-order GridFunction: only its vertex dofs are read
+    src.vec[: mesh.nv] = dev(vals)
+    src.vec[mesh.nv:] = 7.0
+    out = X.ngs.GridFunction(V1)
+    X.xfem.InterpolateToP1(src, out, eps_perturbation=eps)
+    want = np.zeros(mesh.nv)
+    L = orc.load()
+    v = np.ascontiguousarray(vals)
+    L.orc_interpolate_p1_clamp(mesh.nv, orc.P(v), eps, orc.P(want))
+    got = out.vec.cpu().numpy()
+    assert np.array_equal(got.view(np.int64), want.view(np.int64))             # bit-exact, signs of zero included
+    assert (np.abs(got) >= eps).all() and (got[:11] == eps).sum() >= 9
+    # CoefficientFunction branch: x - 1/2 vanishes on a vertex plane of the nx = 4 mesh -> clamped, no degenerate element afterwards
+    out2 = X.ngs.GridFunction(V1)
+    X.xfem.InterpolateToP1(X.ngs.x - 0.5, out2, eps_perturbation=eps)
+    g2 = out2.vec.cpu().numpy()
+    xs = mesh.vert.cpu().numpy()[:, 0]
+    assert np.array_equal(g2[xs == 0.5], np.full((xs == 0.5).sum(), eps)) and np.array_equal(g2[xs != 0.5], (xs - 0.5)[xs != 0.5])
+    ci = X.xfem.CutInfo(mesh, out2)
+    ci.check_degenerate()
+    # without the clamp the same level set is one the reference throws on
+    out3 = X.ngs.GridFunction(V1)
+    X.xfem.InterpolateToP1(X.ngs.x - 0.5, out3, eps_perturbation=0.0)
+    with pytest.raises(X.lib.NgsxError):
+        X.xfem.CutInfo(mesh, out3).check_degenerate()
+
+
+@pytest.mark.parametrize("dim", [2, 3])
+def test_node_marks_against_restatement(X, dim):
+    """cut_neighboring_node / dom_of_node for vertices, edges, faces and cells (xfem/cutinfo.cpp:122-186), node by node"""
+    m = X.meshes.MakeStructured2DMesh(9) if dim == 2 else X.meshes.MakeStructured3DMesh(5)
+    mesh = X.ngs.Mesh(m)
+    gf = X.ngs.GridFunction(X.ngs.H1(mesh, order=1))
+    X.xfem.InterpolateToP1(X.ngs.SphereLevelset((0.47,) * dim, 0.31), gf)
+    ci = X.xfem.CutInfo(mesh, gf)
+    ci.Update(gf, node_marks=True)
+    dom, ratio = ci.dom.cpu().numpy(), ci.ratio.cpu().numpy()
+    assert (dom == IF).any() and (dom == NEG).any() and (dom == POS).any()
+    tables = {"vertex": mesh.el2v.cpu().numpy(), "edge": mesh.edges()[1].cpu().numpy()}
+    if dim == 3:
+        tables["face"] = mesh.faces()[1].cpu().numpy()
+    for name, tab in tables.items():
+        nn = int(tab.max()) + 1
+        cut_nb = np.zeros(nn, dtype=bool)
+        cut_nb[tab[dom == IF].reshape(-1)] = True                              # :133-148
+        don = np.full(nn, IF)
+        for dt in (NEG, POS):                                                  # :163-173 (a node never touches uncut elements of both signs)
+            don[tab[dom == dt].reshape(-1)] = dt
+        assert np.array_equal(ci.cut_neighboring_node[name].to_bool().cpu().numpy(), cut_nb), name
+        assert np.array_equal(ci.dom_of_node[name].cpu().numpy(), don), name
+    assert np.array_equal(ci.cut_neighboring_node["element"].to_bool().cpu().numpy(), dom == IF)
+    want_cell = np.where(dom == IF, IF, np.where(ratio > 0.5, NEG, POS))       # :176-181: cells of uncut elements by the cut ratio
+    assert np.array_equal(ci.dom_of_node["element"].cpu().numpy(), want_cell)
+
+
+@pytest.mark.parametrize("dim", [2, 3])
+def test_order3_single_elements_vertex_permutations(X, golden_single, dim):
+    """order 3: the edge / face functions depend on the orientation given by the GLOBAL vertex numbers
+    (NGS/fem/h1hofe_impl.hpp:78-108, 250-312).  The golden single elements with random global numberings of their vertices,
+    against the oracle (pinned vs the compiled H1HighOrderFE at order 3 with random vertex numbers, tests/test_oracle_vs_ref.py)."""
+    from oracle import orc
+    g = golden_single
+    pm, ls = g[f"d{dim}_pmat"], g[f"d{dim}_lset"]
+    ok = g[f"d{dim}_dom"] >= 0
+    pm, ls = pm[ok][:150], ls[ok][:150]
+    n, nvl = pm.shape[0], dim + 1
+    rng = np.random.default_rng(77 + dim)
+    perm = np.stack([rng.permutation(nvl) for _ in range(n)])                  # local vertex i carries global number e * nvl + perm[e][i]
+    el2v = (np.arange(n)[:, None] * nvl + perm).astype(np.int32)
+    vert = np.zeros((n * nvl, dim))
+    vert[el2v.reshape(-1)] = pm.reshape(-1, dim)
+    lsv = np.zeros(n * nvl)
+    lsv[el2v.reshape(-1)] = ls.reshape(-1)
+    mesh = X.ngs.Mesh(X.meshes.SimplexMesh(dim, torch.as_tensor(vert), torch.as_tensor(el2v)))
+    gf = X.ngs.GridFunction(X.ngs.H1(mesh, order=1))
+    gf.vec.copy_(dev(lsv))
+    Vh = X.ngs.H1(mesh, order=3)
+    u, v = Vh.TnT()
+    for dt in (NEG, POS, IF):
+        a = X.xfem.BilinearForm(Vh)
+        a += X.xfem.SymbolicBFI(levelset_domain={"levelset": gf, "domain_type": dt}, form=0.7 * X.ngs.grad(u) * X.ngs.grad(v) + 1.3 * u * v)
+        els, em, npts = a.elmats()
+        e = els.cpu().numpy()
+        ref, rnp = orc.elmat_mesh(dim, el2v, vert, lsv, 3, dt, 6, 1.3, 0.7, els=e)
+        assert len(e) > 20 and np.array_equal(npts.cpu().numpy(), np.maximum(rnp, 0))
+        assert relerr_rows(em.cpu().numpy(), ref) <= RTOL
+        f = X.xfem.LinearForm(Vh)
+        f += X.xfem.SymbolicLFI(levelset_domain={"levelset": gf, "domain_type": dt}, form=(1.0 + X.ngs.x * X.ngs.y) * v)
+        f.Assemble()
+        want = orc.assemble_vec(dim, el2v, vert, lsv, 3, Vh.el2dof.cpu().numpy(), Vh.ndof, dt, 6, [(1.0, 0, 0, 0), (1.0, 1, 1, 0)])
+        assert np.abs(f.vec.cpu().numpy() - want).max() <= RTOL * np.abs(want).max()

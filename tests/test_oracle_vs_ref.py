@@ -111,3 +111,78 @@ def test_deformed_reduces_to_affine(dim):
                 assert a[0] == b[0]
                 if a[0] > 0:
                     assert np.abs(a[1] - b[1]).max() <= 1e-12 * np.abs(b[1]).max()
+
+
+# ---------------------------------------------------------------------------------------------------------------------
+# rows c-5 / f-1 / f-2 and the Nitsche / normal-normal terms: the restatements against reference code
+# ---------------------------------------------------------------------------------------------------------------------
+def patch_pair(rng, dim):
+    """two simplices sharing a facet, random local vertex orders and global vertex numbers"""
+    pts = np.vstack([np.eye(dim), np.zeros(dim), 0.9 * np.ones(dim)]) + 0.2 * rng.uniform(-1, 1, (dim + 2, dim))
+    pts = pts * rng.uniform(0.05, 0.5) + rng.uniform(-1, 1, dim)
+    glob = rng.permutation(200)[: dim + 2]
+    l1 = rng.permutation(np.arange(dim + 1))                                   # element 1: points 0..dim
+    l2 = rng.permutation(np.array(list(range(1, dim + 1)) + [dim + 1]))        # element 2: shares points 1..dim
+    return glob[l1], pts[l1], glob[l2], pts[l2]
+
+
+@pytest.mark.parametrize("dim", [2, 3])
+@pytest.mark.parametrize("fo", [1, 2, 3])
+def test_facetpatch_against_reference(dim, fo):
+    """orc_facetpatch_elmat_h1 vs the reference's MapPatchIntegrationPoint + H1HighOrderFE (ref_facetpatch_elmat_h1)"""
+    rng = np.random.default_rng(100 * dim + fo)
+    for t in range(60):
+        vn1, p1, vn2, p2 = patch_pair(rng, dim)
+        coef, hpow = rng.uniform(0.1, 2.0), int(rng.integers(-2, 2))
+        na, a = orc.facetpatch_elmat_h1(dim, fo, vn1, p1, vn2, p2, coef, hpow)
+        nb, b = orc.facetpatch_elmat_h1(dim, fo, vn1, p1, vn2, p2, coef, hpow, impl="ref")
+        assert na == nb > 0
+        assert np.abs(a - b).max() <= 1e-12 * np.abs(b).max()
+        assert np.abs(b - b.T).max() <= 1e-13 * np.abs(b).max()
+
+
+@pytest.mark.parametrize("dim", [2, 3])
+@pytest.mark.parametrize("fo", [1, 2])
+def test_xfem_restatement_against_reference_diffopx(dim, fo):
+    """oracle/xfem_ref.py (numpy) vs the reference's DiffOpX<D, RNEG/RPOS/RNEG_GRAD/RPOS_GRAD> on an XFiniteElement"""
+    from oracle import xfem_ref
+    rng = np.random.default_rng(31 * dim + fo)
+    nd = orc.load().orc_h1_ndof(dim, fo)
+    for t in range(60):
+        pm = nice_simplex(rng, dim)
+        vn = rng.permutation(50)[: dim + 1]
+        ls = rng.uniform(-1, 1, dim + 1)
+        if t % 3 == 0:
+            ls = np.abs(ls) * (1 if t % 2 else -1)                           # uncut elements too
+        cut = ls.min() < 0 < ls.max()
+        xs = rng.integers(0, 2, nd) if cut else None
+        kap, alpha = rng.uniform(0, 1), rng.uniform(0.5, 3, 2)
+        a = xfem_ref.nxfem_elmat(dim, fo, vn, pm, ls, xs, kap, alpha, 20.0)
+        b = xfem_ref.nxfem_elmat_ref(dim, fo, vn, pm, ls, xs, kap, alpha, 20.0)
+        assert a.shape == b.shape and np.abs(a - b).max() <= 1e-12 * max(np.abs(b).max(), 1e-300)
+        fp = {(0, 0, 0): 1.0, (1, 0, 0): 0.5, (0, 2, 0): -0.25}
+        for dt in (0, 1):
+            va = xfem_ref.nxfem_elvec(dim, fo, vn, pm, ls, xs, dt, fp)
+            vb = xfem_ref.nxfem_elvec_ref(dim, fo, vn, pm, ls, xs, dt, fp)
+            assert np.abs(va - vb).max() <= 1e-12 * max(np.abs(vb).max(), 1e-300)
+
+
+@pytest.mark.parametrize("dim", [2, 3])
+@pytest.mark.parametrize("dord", [1, 2])
+def test_general_form_against_reference(dim, dord):
+    """Nitsche, normal-normal and mesh_size terms of ngsx_form_h1 (restated in orc_elmat_h1_iso) vs ref_elmat_h1_form: the
+    reference's rule, mapped points, shapes, mapped gradients, P1 level-set gradient and per-point mesh_size"""
+    rng = np.random.default_rng(17 * dim + dord)
+    forms = [orc.form8(1.3, 0.7), orc.form8(10.0, 0.0, -1.0, 0.5, hpow=(-1, 0, 0, 0)), orc.form8(0.0, 1.0, 0.0, -1.0),
+             orc.form8(0.3, 0.2, 0.9, 0.4, hpow=(1, -2, -1, 2))]
+    for t in range(30):
+        gc = iso_coefs(rng, dim, dord)
+        ls = rng.uniform(-1, 1, dim + 1)
+        for fo in (1, 2):
+            for dt in (0, 1, 2):
+                for f in forms:
+                    na, a = orc.elmat_h1_iso(dim, fo, dord, gc, ls, dt, 2 * fo, f)
+                    nb, b = orc.elmat_h1_form(dim, fo, None, gc, ls, dt, 2 * fo, f, dord=dord)
+                    assert na == nb
+                    if na > 0:
+                        assert np.abs(a - b).max() <= 1e-12 * np.abs(b).max()
