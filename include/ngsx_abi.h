@@ -179,8 +179,9 @@ int ngsx_assemble_vec_h1(const ngsx_mesh *mesh, const double *lset_v, int fe_ord
  * contributions of one entry are summed in list order by a single warp, so the values are bitwise reproducible and no
  * floating-point atomic is used.  Multi-GPU: a plan restricted to rows [row_lo, row_hi) makes the rank the owner of those
  * rows -- it recomputes the halo elements listed in `table` instead of exchanging interface rows.
- * table [nlist][nd]: dofs of list entry k (list order fixes the summation order), nd <= 27, the nd dofs of one entry
- * distinct; rows longer than 256 entries are NGSX_ERR_UNSUPPORTED (use the coloured path). */
+ * table [nlist][nd]: dofs of list entry k (list order fixes the summation order), nd <= 26, nlist < 2^27, the nd dofs of one
+ * entry distinct; CSR rows longer than 256 entries and dofs with more than 255 adjacent list entries are NGSX_ERR_UNSUPPORTED
+ * (use the coloured path).  The plan is a static schedule (tiles of rows -> lanes -> steps, ngsxfem_b200/csrc/ngsx_rows.cuh). */
 typedef struct ngsx_rowplan ngsx_rowplan;   /* opaque, owns device buffers (pair descriptors, geometry factors, cut-element matrices) */
 int ngsx_rowplan_create(int64_t nlist, int32_t nd, const int32_t *table, int64_t ndof, const int64_t *rowptr, const int32_t *colidx,
                         int64_t row_lo, int64_t row_hi, ngsx_rowplan **out, void *stream);
@@ -195,6 +196,12 @@ int ngsx_rowplan_create_owned(int64_t nlist, int32_t nd, const int32_t *table, i
  * entry, one past the last covered CSR entry} */
 int ngsx_rowplan_info(const ngsx_rowplan *plan, int64_t *h_info);
 int ngsx_rowplan_destroy(ngsx_rowplan *plan);
+/* Cut-element buffer of ngsx_assemble_csr_rows_h1: sized by a counting pass on the plan's first numeric call (elements that
+ * need quadrature + 25 %), reused afterwards.  ngsx_rowplan_cut_usage (synchronises the stream) returns the number of
+ * quadrature elements the LAST call met and the capacity; count > capacity means that call skipped the excess elements
+ * (the level set moved a lot): reserve more with ngsx_rowplan_reserve_cut and assemble again. */
+int ngsx_rowplan_cut_usage(ngsx_rowplan *plan, int64_t *h_count, int64_t *h_capacity, void *stream);
+int ngsx_rowplan_reserve_cut(ngsx_rowplan *plan, int64_t capacity);
 /* els [nlist]: element numbers of the list entries (same order as `table` at plan creation).  Elements whose cut rule is
  * empty for (dt) contribute nothing (the reference's `ir == nullptr` return, xfem/symboliccutbfi.cpp:119-120).
  * accumulate == 0: rows of the plan are overwritten; != 0: added to.  err as in ngsx_classify (may be NULL). */
@@ -212,6 +219,17 @@ void ngsx_set_gather_wait_event(void *event);
  * blocks of the plan's list entries (elements, or facet patches with their merged dof lists) are gathered row by row;
  * accumulate as above.  nd in {3, 4, 5, 6, 8, 9, 10, 12, 14, 20}. */
 int ngsx_assemble_csr_rows_mats(ngsx_rowplan *plan, const double *mats, int accumulate, double *vals, void *stream);
+/* PACKED block rows: the fast form of the call above.  ngsx_rowplan_rowslots returns rowslot [nlist][nd] (device, owned by the
+ * plan; built on the first request, synchronises): slot of the pair (list entry k, local row i) in the plan's schedule, -1 if the
+ * row is not covered, and the number of slots.  A producer kernel writes row i of block k to rows + slot * ndp, ndp = nd rounded
+ * up to even (ngsx_set_packed_output makes the block-producing entry points of this library do that); rows [nslots][ndp] must
+ * be 16-byte aligned.  The rows a warp needs in one step are then contiguous: every byte is read once, in whole lines. */
+int ngsx_rowplan_rowslots(ngsx_rowplan *plan, const int32_t **d_rowslot, int64_t *h_nslots, void *stream);
+int ngsx_assemble_csr_rows_packed(ngsx_rowplan *plan, const double *rows, int accumulate, double *vals, void *stream);
+/* One-shot, like ngsx_set_gather_wait_event: the NEXT block-producing call of this host thread (ngsx_elmat_h1_deformed,
+ * ngsx_facetpatch_cmat_h1, ngsx_xfem_elmat_h1) writes its blocks as packed rows -- its output pointer is then the rows buffer
+ * of ngsx_assemble_csr_rows_packed.  NULL clears. */
+void ngsx_set_packed_output(const int32_t *d_rowslot);
 /* The same for vectors (AddElementVector, NGS/comp/linearform.cpp:209-243, without atomics): out[d] (+)= scale * sum of
  * src[pairs[p]] over p in [dofptr[d], dofptr[d+1]), in list order.  src: flattened element vectors (e.g. of ngsx_elvec_h1),
  * pairs: indices into it grouped by dof -- entries a sign mask removes (DiffOpX, xfem/xfemdiffops.cpp:30-40) are simply not

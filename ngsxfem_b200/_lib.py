@@ -79,6 +79,11 @@ SIGNATURES = {
     "ngsx_rowplan_create_owned": (c_int, [c_i64, c_i32, c_void_p, c_i64, c_void_p, c_void_p, c_void_p, c_i32, ctypes.POINTER(c_void_p), c_void_p]),
     "ngsx_rowplan_info": (c_int, [c_void_p, ctypes.POINTER(c_i64)]),
     "ngsx_rowplan_destroy": (c_int, [c_void_p]),
+    "ngsx_rowplan_cut_usage": (c_int, [c_void_p, ctypes.POINTER(c_i64), ctypes.POINTER(c_i64), c_void_p]),
+    "ngsx_rowplan_reserve_cut": (c_int, [c_void_p, c_i64]),
+    "ngsx_rowplan_rowslots": (c_int, [c_void_p, ctypes.POINTER(c_void_p), ctypes.POINTER(c_i64), c_void_p]),
+    "ngsx_assemble_csr_rows_packed": (c_int, [c_void_p, c_void_p, c_int, c_void_p, c_void_p]),
+    "ngsx_set_packed_output": (None, [c_void_p]),
     "ngsx_assemble_csr_rows_h1": (c_int, [ctypes.POINTER(Mesh), c_void_p, c_int, c_int, c_int, ctypes.POINTER(FormH1), c_i64, c_void_p,
                                           c_void_p, c_int, c_void_p, c_void_p, c_void_p]),
     "ngsx_set_gather_wait_event": (None, [c_void_p]),

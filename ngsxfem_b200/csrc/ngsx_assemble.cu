@@ -165,7 +165,7 @@ __global__ void __launch_bounds__(WARPS * 32) k_elmat(ElmatArgs A, int64_t first
     }
   }
 
-  if (A.d_count) count = *A.d_count;
+  if (A.d_count) count = min(count, (int64_t)*A.d_count);      // work list on the device, clamped to the caller's capacity
   const int64_t ngroups = (count + A.group - 1) / A.group;
   const int64_t nwarps = (int64_t)gridDim.x * WARPS;
   for (int64_t g = (int64_t)blockIdx.x * WARPS + warp; g < ngroups; g += nwarps) {
@@ -572,73 +572,16 @@ static int dispatch_elvec(const ElvecArgs &A, int fe_order, int sm_count, int nc
 // ---------------------------------------------------------------------------------------------------------------
 // feeders of the owner-computes row gather (ngsx_rows.cu)
 // ---------------------------------------------------------------------------------------------------------------
-// reference tables of the constant-rule path: tab[q][i][j] = sum_r w_r (d_a phi_i d_b phi_j [+ d_b phi_i d_a phi_j]) for the
-// q-th pair a <= b, tab[NPAIR][i][j] = sum_r w_r phi_i phi_j, over the reference rule of the requested order
-template <int DIM, int ORDER>
-__global__ void __launch_bounds__(128) k_ref_tables(const double4 *__restrict__ rule, int nr, double *__restrict__ tab) {
-  constexpr int ND = H1<DIM, ORDER>::ND, NE = ND * ND, CS = RefTab<DIM>::CS;
-  double glr[DIM + 1][DIM];
-#pragma unroll
-  for (int k = 0; k <= DIM; k++)
-#pragma unroll
-    for (int d = 0; d < DIM; d++) glr[k][d] = (k == DIM) ? -1.0 : (k == d ? 1.0 : 0.0);
-  // mass table  Tm[i][j] = sum_r w_r phi_i phi_j
-  for (int idx = threadIdx.x; idx < NE; idx += blockDim.x) {
-    const int i = idx / ND, j = idx % ND;
-    double acc = 0.0;
-    for (int q = 0; q < nr; q++) {
-      const double4 r = rule[q];
-      double lam[4] = {r.x, r.y, r.z, 0.0};
-      double last = 1.0;
-#pragma unroll
-      for (int k = 0; k < DIM; k++) last -= lam[k];
-      lam[DIM] = last;
-      acc += r.w * h1_shape<DIM, ORDER>(i, lam) * h1_shape<DIM, ORDER>(j, lam);
-    }
-    tab[idx] = acc;
-  }
-  // gradient-moment table.  The reference gradients of P1/P2 shapes are affine: d_a phi_i = sum_m c_m X_m, X = (1, x, y[, z]);
-  // cM[i][a][n] = sum_m c_m M_mn with the rule's moments M_mn = sum_r w_r X_m X_n.
-  for (int idx = threadIdx.x; idx < ND * DIM; idx += blockDim.x) {
-    const int i = idx / DIM, a = idx % DIM;
-    double c[DIM + 1];
-    {
-      double lam[4] = {0.0, 0.0, 0.0, 0.0};
-      lam[DIM] = 1.0;
-      double sv, g0[DIM];
-      h1_shape_grad<DIM, ORDER>(i, lam, glr, sv, g0);
-      c[0] = g0[a];
-      for (int m = 0; m < DIM; m++) {
-        double l2[4] = {0.0, 0.0, 0.0, 0.0};
-        l2[m] = 1.0;
-        double gm[DIM];
-        h1_shape_grad<DIM, ORDER>(i, l2, glr, sv, gm);
-        c[m + 1] = gm[a] - g0[a];
-      }
-    }
-    for (int n = 0; n <= DIM; n++) {
-      double s = 0.0;
-      for (int m = 0; m <= DIM; m++) {
-        double mom = 0.0;
-        for (int q = 0; q < nr; q++) {
-          const double4 r = rule[q];
-          const double X[4] = {1.0, r.x, r.y, r.z};
-          mom += r.w * X[m] * X[n];
-        }
-        s += c[m] * mom;
-      }
-      tab[RefTab<DIM>::cm_offset(NE) + i * CS + a * (DIM + 1) + n] = s;
-    }
-  }
-}
-
-// one thread per list entry: sign test, then either the 7 geometry factors of the constant-rule path or a slot in the
+// one thread per list entry: sign test, then either the geometry record of the constant-rule path or a slot in the
 // quadrature work list.  The slot order depends on the atomic counter, the values do not.
+// Geometry record of list entry k (ngsx_rows.cuh): per local vertex a the 32 bytes {K[a][0..DIM-1], (pad), gm},
+//   K[a][b] = |det J| c_s grad(lam_a).grad(lam_b) (physical gradients: rows of J^-1, grad(lam_DIM) = -sum), gm = |det J| c_m.
+// A vertex row of the element matrix needs record a alone, an edge row the records of its two vertices (k_rows).  Entries that
+// contribute nothing, or whose matrix comes from the quadrature kernel, carry a NaN-boxed code in the gm slot of every record.
 template <int DIM>
 __global__ void __launch_bounds__(256) k_geom(ngsx_mesh M, const double *__restrict__ lset, const int32_t *__restrict__ els, int64_t nlist,
                                              int dt, FormDev form, int use_fast, double *__restrict__ G, int32_t *__restrict__ cutlist,
-                                             int32_t *__restrict__ cutcount, unsigned long long *__restrict__ err) {
-  constexpr int NPAIR = DIM * (DIM + 1) / 2;
+                                             int32_t *__restrict__ cutcount, int64_t cut_cap, unsigned long long *__restrict__ err) {
   int64_t k = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (k >= nlist) return;
   const int64_t e = els ? els[k] : k;
@@ -646,10 +589,10 @@ __global__ void __launch_bounds__(256) k_geom(ngsx_mesh M, const double *__restr
   load_el<DIM>(M, lset, e, ls, p);
   int mask;
   const int dom = sign_test<DIM>(ls, mask);
-  double g[GSTRIDE];
+  double Kr[DIM + 1][3];
 #pragma unroll
-  for (int q = 0; q < GSTRIDE; q++) g[q] = 0.0;
-  long long code = -1;
+  for (int a = 0; a <= DIM; a++) Kr[a][0] = Kr[a][1] = Kr[a][2] = 0.0;
+  double gm = __longlong_as_double((long long)GCODE_NAN);                // payload 0: no contribution
   if (dom == -1) {
     if (err) {
       atomicAdd(&err[0], 1ULL);
@@ -665,34 +608,32 @@ __global__ void __launch_bounds__(256) k_geom(ngsx_mesh M, const double *__restr
         double h = DIM == 2 ? sqrt(meas) : cbrt(meas);
         cm *= ipow(h, form.pm); cs *= ipow(h, form.ps);
       }
-      int pr = 0;
+      const double f = meas * cs;
 #pragma unroll
-      for (int a = 0; a < DIM; a++)
+      for (int b = 0; b < DIM; b++) {
+        double col = 0.0;
 #pragma unroll
-        for (int b = a; b < DIM; b++) {
+        for (int a = 0; a < DIM; a++) {
           double s = 0.0;
 #pragma unroll
           for (int d = 0; d < DIM; d++) s += Gm.Jinv[a][d] * Gm.Jinv[b][d];
-          g[pr++] = meas * cs * s;
+          Kr[a][b] = f * s;
+          col += f * s;
         }
-      static_assert(NPAIR <= 6, "geometry record too small");
-      g[6] = meas * cm;
-      code = 0;
+        Kr[DIM][b] = -col;
+      }
+      gm = meas * cm;
     } else {
-      int slot = atomicAdd(cutcount, 1);
-      cutlist[slot] = (int32_t)k;
-      code = (long long)slot + 1;
+      const int slot = atomicAdd(cutcount, 1);                           // beyond the capacity: counted (the caller grows the buffer), skipped
+      if (slot < cut_cap) {
+        cutlist[slot] = (int32_t)k;
+        gm = __longlong_as_double((long long)(GCODE_NAN | (unsigned long long)(slot + 1)));
+      }
     }
   }
-  g[7] = __longlong_as_double(code);
-  double4 *out = reinterpret_cast<double4 *>(G + k * GSTRIDE);
-  out[0] = make_double4(g[0], g[1], g[2], g[3]);
-  out[1] = make_double4(g[4], g[5], g[6], g[7]);
-}
-
-template <int DIM, int ORDER>
-static void launch_ref_tables(const double4 *rule, int nr, double *tab, cudaStream_t st) {
-  k_ref_tables<DIM, ORDER><<<1, 128, 0, st>>>(rule, nr, tab);
+  double4 *out = reinterpret_cast<double4 *>(G + k * ((DIM + 1) * 4));
+#pragma unroll
+  for (int a = 0; a <= DIM; a++) out[a] = make_double4(Kr[a][0], Kr[a][1], Kr[a][2], gm);
 }
 
 // ---------------------------------------------------------------------------------------------------------------
@@ -716,7 +657,7 @@ __global__ void __launch_bounds__(CUTMAT_THREADS) k_cutmat(ElmatArgs A, int64_t 
   for (int i = threadIdx.x; i < A.nr_if; i += blockDim.x) srule_if[i] = A.rule_if[i];
   if (threadIdx.x < 16) lut[threadIdx.x] = A.tab->e[DIM - 2][A.dt][threadIdx.x];
   __syncthreads();
-  if (A.d_count) count = *A.d_count;
+  if (A.d_count) count = min(count, (int64_t)*A.d_count);      // work list on the device, clamped to the caller's capacity
   for (int64_t s = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; s < count; s += (int64_t)gridDim.x * blockDim.x) {
     const int64_t kk = A.sublist ? A.sublist[s] : s;
     const int64_t e = A.els ? A.els[kk] : kk;
@@ -865,7 +806,7 @@ __global__ void __launch_bounds__(CUTMAT_THREADS) k_cutmat_mom(ElmatArgs A, int6
   for (int i = threadIdx.x; i < A.nr_if; i += blockDim.x) srule_if[i] = A.rule_if[i];
   if (threadIdx.x < 16) lut[threadIdx.x] = A.tab->e[DIM - 2][A.dt][threadIdx.x];
   __syncthreads();
-  if (A.d_count) count = *A.d_count;
+  if (A.d_count) count = min(count, (int64_t)*A.d_count);      // work list on the device, clamped to the caller's capacity
   for (int64_t s = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; s < count; s += (int64_t)gridDim.x * blockDim.x) {
     const int64_t kk = A.sublist ? A.sublist[s] : s;
     const int64_t e = A.els ? A.els[kk] : kk;
@@ -1118,6 +1059,7 @@ int ngsx_elmat_h1(const ngsx_mesh *mesh, const double *lset_v, int fe_order, int
   fill_form(h_form, A.form);
   A.els = els; A.group = 1; A.use_fast = g_use_fast && h_form->c_nitsche == 0.0 && h_form->c_dndn == 0.0;
   A.elmats = elmats; A.npts = npts;
+  if (take_packed_output()) { set_error("elmat_h1: packed output is not served by this entry point yet"); return NGSX_ERR_UNSUPPORTED; }
   return dispatch_elmat<0>(A, fe_order, dd->sm_count, 1, nullptr, nlist, as_stream(stream));
 }
 
@@ -1149,34 +1091,47 @@ int ngsx_assemble_csr_rows_h1(const ngsx_mesh *mesh, const double *lset_v, int f
   NGSX_REQUIRE(h_form && plan && nlist >= 0 && nlist == plan->nlist, "assemble_csr_rows_h1: bad arguments (nlist must match the plan)");
   NGSX_REQUIRE(plan->nrows == 0 || vals, "assemble_csr_rows_h1: vals is NULL");
   if (int rc = fill_common(mesh, lset_v, fe_order, dt, intorder, &dd, &rv, &nv, &ri, &ni)) return rc;
-  const int dim = mesh->dim, npairtab = dim * (dim + 1) / 2;
+  const int dim = mesh->dim;
   const int nd = dim == 2 ? (fe_order == 1 ? 3 : 6) : (fe_order == 1 ? 4 : 10);
   NGSX_REQUIRE(nd == plan->nd, "assemble_csr_rows_h1: the plan was built for another element type");
   cudaStream_t st = as_stream(stream);
   if (err) { if (int rc = reset_err(err, st)) return rc; }
   if (nlist == 0 || plan->nrows == 0) return NGSX_OK;
-  if (int rc = rows_scratch(plan, npairtab)) return rc;
+  if (int rc = rows_scratch(plan, dim)) return rc;
   FormDev form;
   fill_form(h_form, form);
-  const int use_fast = g_use_fast && h_form->c_nitsche == 0.0 && h_form->c_dndn == 0.0 && dt != IF;
-  // 1. reference tables (tiny), 2. geometry factors + quadrature work list, 3. cut-element matrices, 4. row gather
+  // the closed-form rows of the gather need a permutation-symmetric reference rule (the tabulated NGSolve simplex rules of the
+  // orders P1 / P2 forms use are); otherwise, and for forms with normal derivatives / interface integrals, every contributing
+  // element goes through the quadrature kernel
+  RuleMom mom{};
+  const bool sym_rule = rule_moments(dim, intorder, &mom);
+  const int use_fast = g_use_fast && sym_rule && h_form->c_nitsche == 0.0 && h_form->c_dndn == 0.0 && dt != IF;
+  // 1. geometry records + quadrature work list, 2. cut-element matrices, 3. row gather
   if (g_timing) { g_ev = g_evr[g_ev_calls % TIMING_RING]; g_ev_calls++; cudaEventRecord(g_ev[0], st); }
-  if (plan->tab_rule != rv || plan->tab_key != dim * 1000 + fe_order * 100 + nv) {      // calls on one plan are stream-ordered by the caller
-    switch (dim * 10 + fe_order) {
-      case 21: launch_ref_tables<2, 1>(rv, nv, plan->tab, st); break;
-      case 22: launch_ref_tables<2, 2>(rv, nv, plan->tab, st); break;
-      case 31: launch_ref_tables<3, 1>(rv, nv, plan->tab, st); break;
-      case 32: launch_ref_tables<3, 2>(rv, nv, plan->tab, st); break;
-    }
-    NGSX_LAUNCH_CHECK();
-    plan->tab_rule = rv; plan->tab_key = dim * 1000 + fe_order * 100 + nv;
-  }
-  NGSX_CUDA(cudaMemsetAsync(plan->cutcount, 0, sizeof(int32_t), st));
   auto *e = reinterpret_cast<unsigned long long *>(err);
   const unsigned nb = (unsigned)((nlist + 255) / 256);
-  if (dim == 2) k_geom<2><<<nb, 256, 0, st>>>(*mesh, lset_v, els, nlist, dt, form, use_fast, plan->G, plan->cutlist, plan->cutcount, e);
-  else k_geom<3><<<nb, 256, 0, st>>>(*mesh, lset_v, els, nlist, dt, form, use_fast, plan->G, plan->cutlist, plan->cutcount, e);
-  NGSX_LAUNCH_CHECK();
+  auto geom = [&]() -> int {
+    NGSX_CUDA(cudaMemsetAsync(plan->cutcount, 0, sizeof(int32_t), st));
+    if (dim == 2) k_geom<2><<<nb, 256, 0, st>>>(*mesh, lset_v, els, nlist, dt, form, use_fast, plan->G, plan->cutlist, plan->cutcount, plan->cut_cap, e);
+    else k_geom<3><<<nb, 256, 0, st>>>(*mesh, lset_v, els, nlist, dt, form, use_fast, plan->G, plan->cutlist, plan->cutcount, plan->cut_cap, e);
+    NGSX_LAUNCH_CHECK();
+    return NGSX_OK;
+  };
+  if (plan->cut_cap == 0 || (!use_fast && plan->cut_cap < nlist)) {
+    // First numeric call on this plan: size the cut-element buffer from a counting pass (synchronises once; not capturable).
+    // Later calls reuse it; a level set that needs more reports through ngsx_rowplan_cut_usage (count > capacity).
+    int64_t want = nlist;
+    if (use_fast) {
+      if (int rc = geom()) return rc;
+      int32_t c = 0;
+      NGSX_CUDA(cudaMemcpyAsync(&c, plan->cutcount, sizeof c, cudaMemcpyDeviceToHost, st));
+      NGSX_CUDA(cudaStreamSynchronize(st));
+      want = (int64_t)c + c / 4 + 1024;
+      if (err) { if (int rc = reset_err(err, st)) return rc; }
+    }
+    if (int rc = rows_reserve_cut(plan, want)) return rc;
+  }
+  if (int rc = geom()) return rc;
   if (g_timing) cudaEventRecord(g_ev[1], st);
   ElmatArgs A{};
   A.M = *mesh; A.lset = lset_v; A.tab = dd->cut_table; A.dt = dt;
@@ -1185,10 +1140,10 @@ int ngsx_assemble_csr_rows_h1(const ngsx_mesh *mesh, const double *lset_v, int f
   A.els = els; A.sublist = plan->cutlist; A.d_count = plan->cutcount; A.group = 1; A.use_fast = 0;
   A.elmats = plan->cutmats; A.npts = nullptr;
   // the work-list length lives on the device: launch the persistent grid for the worst case, idle CTAs leave at once
-  if (int rc = launch_cutmat(A, fe_order, dd->sm_count, nlist, st)) return rc;
+  if (int rc = launch_cutmat(A, fe_order, dd->sm_count, plan->cut_cap, st)) return rc;
   if (gather_wait) NGSX_CUDA(cudaStreamWaitEvent(st, gather_wait, 0));      // the gather starts once the caller's side work is done
   if (g_timing) cudaEventRecord(g_ev[2], st);
-  const int rc = launch_rows(plan, npairtab, accumulate, vals, dd->sm_count, st);
+  const int rc = launch_rows(plan, dim, mom, accumulate, vals, dd->sm_count, st);
   if (g_timing) cudaEventRecord(g_ev[3], st);
   return rc;
 }

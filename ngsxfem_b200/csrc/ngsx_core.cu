@@ -117,6 +117,13 @@ const DeviceData *device_data() {
   return &g_dd[dev];
 }
 
+static thread_local const int32_t *g_packed_output = nullptr;
+const int32_t *take_packed_output() {
+  const int32_t *p = g_packed_output;
+  g_packed_output = nullptr;
+  return p;
+}
+
 bool rule_lookup(const DeviceData *dd, int sdim, int order, const double4 **ptr, int *n) {
   if (order < 0) order = 0;
   const int *offs = nullptr;
@@ -758,6 +765,8 @@ using namespace ngsx;
 static inline unsigned nblocks(int64_t n, int bs) { return (unsigned)((n + bs - 1) / bs); }
 
 extern "C" {
+
+void ngsx_set_packed_output(const int32_t *d_rowslot) { ngsx::g_packed_output = d_rowslot; }
 
 int ngsx_abi_version(void) { return NGSX_ABI_VERSION; }
 const char *ngsx_last_error(void) { return t_err.c_str(); }

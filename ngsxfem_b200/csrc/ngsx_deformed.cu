@@ -43,6 +43,7 @@ struct DefArgs {
   PolyDevD f;
   const int32_t *els;
   double *elmats; int32_t *npts;       // element matrices
+  const int32_t *rowslot;              // packed output (ngsx_set_packed_output): row i of block k -> elmats + rowslot[k nd + i] * ndp
   double *partial;                     // Integrate: one value per element
   unsigned long long *err;
   int32_t *worklist; int32_t *wcount;  // thread-per-element passes: list positions of the cut elements, their number
@@ -407,8 +408,19 @@ __global__ void __launch_bounds__(TT) k_elmat_def_t(DefArgs A, int64_t count) {
         continue;
       }
       if (dom != A.dt) {
+        if (A.rowslot) {
+          constexpr int NDP = ND + (ND & 1);
+          for (int i = 0; i < ND; i++) {
+            const int slot = __ldg(A.rowslot + k * ND + i);
+            if (slot < 0) continue;
+            double *o = A.elmats + (int64_t)slot * NDP;
+#pragma unroll
+            for (int j = 0; j < NDP; j++) o[j] = 0.0;
+          }
+        } else {
 #pragma unroll 4
-        for (int t = 0; t < NE; t++) out[t] = 0.0;
+          for (int t = 0; t < NE; t++) out[t] = 0.0;
+        }
         if (A.npts) A.npts[k] = 0;
         continue;
       }
@@ -511,7 +523,19 @@ __global__ void __launch_bounds__(TT) k_elmat_def_t(DefArgs A, int64_t count) {
     }
     {                                                                   // mirrored store of the symmetric block
       auto tri = [](int i, int j) { return i >= j ? i * (i + 1) / 2 + j : j * (j + 1) / 2 + i; };
-      if constexpr (NE % 2 == 0) {                                      // 16-byte stores: the block starts 16-byte aligned (NE even)
+      if (A.rowslot) {                                                  // packed rows: row i to the slot of the pair (k, i)
+        constexpr int NDP = ND + (ND & 1);
+#pragma unroll
+        for (int i = 0; i < ND; i++) {
+          const int slot = __ldg(A.rowslot + k * ND + i);
+          if (slot >= 0) {
+            double2 *o2 = reinterpret_cast<double2 *>(A.elmats + (int64_t)slot * NDP);
+#pragma unroll
+            for (int j = 0; j < NDP / 2; j++)
+              o2[j] = make_double2(acc[tri(i, 2 * j)], 2 * j + 1 < ND ? acc[tri(i, 2 * j + 1)] : 0.0);
+          }
+        }
+      } else if constexpr (NE % 2 == 0) {                                      // 16-byte stores: the block starts 16-byte aligned (NE even)
         double2 *o2 = reinterpret_cast<double2 *>(out);
 #pragma unroll
         for (int t = 0; t < NE / 2; t++)
@@ -870,6 +894,8 @@ extern "C" int ngsx_elmat_h1_deformed(const ngsx_mesh *mesh, const ngsx_deformat
   A.form.c[0] = h_form->c_mass; A.form.c[1] = h_form->c_stiff; A.form.c[2] = h_form->c_nitsche; A.form.c[3] = h_form->c_dndn;
   A.form.p[0] = h_form->hpow_mass; A.form.p[1] = h_form->hpow_stiff; A.form.p[2] = h_form->hpow_nitsche; A.form.p[3] = h_form->hpow_dndn;
   A.els = els; A.elmats = elmats; A.npts = npts; A.err = reinterpret_cast<unsigned long long *>(err);
+  A.rowslot = take_packed_output();
+  if (A.rowslot && g_def_warp) { set_error("elmat_h1_deformed: packed output is served by the thread-per-element kernels only"); return NGSX_ERR_UNSUPPORTED; }
   switch (mesh->dim * 100 + fe_order * 10 + defo->order) {
     case 211: return launch_elmat_def<2, 1, 1>(A, dd->sm_count, nlist, st);
     case 212: return launch_elmat_def<2, 1, 2>(A, dd->sm_count, nlist, st);

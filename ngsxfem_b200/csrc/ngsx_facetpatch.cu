@@ -307,6 +307,7 @@ extern "C" int ngsx_facetpatch_cmat_h1(const ngsx_mesh *mesh, int fe_order, doub
   if (!dd) return NGSX_ERR_CUDA;
   const double4 *rule; int nr;
   if (!rule_lookup(dd, mesh->dim, 2 * fe_order, &rule, &nr)) { set_error("facetpatch_cmat: rule not tabulated"); return NGSX_ERR_UNSUPPORTED; }
+  if (take_packed_output()) { set_error("packed output is not served by this entry point yet"); return NGSX_ERR_UNSUPPORTED; }
   if (npatch == 0) return NGSX_OK;
   cudaStream_t st = as_stream(stream);
   switch (mesh->dim * 10 + fe_order) {

@@ -49,6 +49,9 @@ const DeviceData *device_data();
 // reference rule of a simplex of dimension sdim (0..3): device pointer and size; false if the order is not tabulated
 bool rule_lookup(const DeviceData *dd, int sdim, int order, const double4 **ptr, int *n);
 
+// one-shot packed-output request of ngsx_set_packed_output: returns the row-slot map (or nullptr) and clears it
+const int32_t *take_packed_output();
+
 inline cudaStream_t as_stream(void *s) { return reinterpret_cast<cudaStream_t>(s); }
 
 }  // namespace ngsx

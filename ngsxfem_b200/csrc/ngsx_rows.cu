@@ -1,26 +1,36 @@
-// ngsx_rows.cu -- (d') owner-computes assembly: plan construction and the row-gather kernel.
+// ngsx_rows.cu -- (d') owner-computes assembly: plan construction (a static schedule) and the row-gather kernel.
 //
 // The coloured scatter (ngsx_assemble.cu) streams the whole CSR value array once per colour: on the 10M-tet config every
 // 32-byte sector of the 584 MB value array is read and written by ~13 different launches.  Here the dependency is turned
-// around: the plan lists, for every non-empty CSR row, the (element, local row) pairs that contribute to it, and ONE WARP
-// gathers a row completely -- contributions are summed in list order in shared memory and each value leaves the SM once,
-// as a coalesced store.  Constant-rule (uncut) elements are recomputed on the fly from 7 geometry factors per element
-// (56 B, L2-resident) contracted with per-CTA reference tables; cut elements read their row of a compact element-matrix
-// buffer produced by the quadrature kernel.  No colouring, no zero-fill, no read-modify-write, no floating-point atomics.
+// around: the plan lists, for every non-empty CSR row, the (element, local row) pairs that contribute to it, and ONE LANE
+// gathers a row completely -- contributions are summed in plan order in the warp's shared-memory window and each value leaves
+// the SM once, as a coalesced store.  No colouring, no zero-fill, no read-modify-write of global memory, no floating-point
+// atomics; the summation order of every CSR entry is fixed by the plan, so the result is bitwise reproducible.
 //
-// Work decomposition of the row kernel: warp = tile of consecutive rows (values in the warp's shared-memory window), lane =
-// contiguous range of the tile's rows (see k_rows).
-// HBM traffic per P2 tet pair: 16 B descriptor + (L2) 64 B factors; per CSR entry: 8 B written once.
+// Second generation (round 2).  The first one (per-row records, per-lane row ranges, reference tables in shared memory) ran at
+// 26 % of the HBM peak by its real traffic: ncu showed the LSU / shared-memory pipe 86 % busy -- per pair two 32-byte loads of
+// a 64-byte geometry record, a 16-byte descriptor load from a lane-private address, ~11 128-bit table reads and 20 scattered
+// 8-byte window accesses.  Now:
+//   * descriptors are stored in the order the warp consumes them (step-major, lane-minor, no padding): one coalesced 128-bit
+//     load per step instead of 32 distinct lines, and no row records / split tables at all (ngsx_rows.cuh);
+//   * rows inside a tile are dealt to the lanes by decreasing pair count (LPT), so the lanes of a tile finish together;
+//   * the constant-rule row of an uncut element is computed WITHOUT tables: for the permutation-symmetric NGSolve rules the
+//     row of the P1/P2 element matrix is a closed form in the rule's moments (kernel constants) and in the rows
+//     K[a][.] = grad(lam_a) G grad(lam_.) of the element's geometry record, which k_geom stores per local vertex (32 bytes) --
+//     a vertex row loads ONE 32-byte record, an edge row two, and no shared-memory table is read;
+//   * cut elements read their row of the compact quadrature buffer as before.
 #include <cub/cub.cuh>
+#include <algorithm>
+#include <numeric>
 #include <vector>
 #include <thrust/iterator/counting_iterator.h>
 #include "ngsx_rows.cuh"
+#include "rule_tables.h"
 
 namespace ngsx {
 
 // ---- plan construction --------------------------------------------------------------------------------------------
-// key = (row, local row i, list index k): the pairs of a row are walked grouped by i, so that the lanes of a warp mostly
-// read the same rows of the reference tables in the same step (shared-memory broadcast instead of distinct wavefronts)
+// key = (row, local row i, list index k): the pairs of a row are walked grouped by i (plan order = summation order)
 __global__ void __launch_bounds__(256) k_pair_keys(int64_t npairs, int nd, int64_t nlist, const int32_t *__restrict__ table, int64_t row_lo,
                                                   int64_t row_hi, const int32_t *__restrict__ row_owner, int32_t me, uint64_t *__restrict__ keys) {
   int64_t p = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
@@ -47,15 +57,15 @@ __global__ void __launch_bounds__(256) k_head_flags(int64_t n, const uint64_t *_
   flags[p] = (p == 0) || ((keys[p] >> 32) != (keys[p - 1] >> 32));
 }
 
-// rows[q] = row of the first pair of run q; closes pairptr; row statistics
+// per plan row: CSR span {rowptr[r], rowptr[r+1]}; closes pairptr; row statistics
 __global__ void __launch_bounds__(256) k_plan_rows(int64_t nrows, int64_t npairs, const uint64_t *__restrict__ keys, int64_t *__restrict__ pairptr,
-                                                  const int64_t *__restrict__ rowptr, int32_t *__restrict__ rows,
+                                                  const int64_t *__restrict__ rowptr, int64_t *__restrict__ span,
                                                   unsigned long long *__restrict__ stat /* {covered, maxlen, lo, hi} */) {
   int64_t q = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (q == 0) pairptr[nrows] = npairs;
   if (q >= nrows) return;
   int32_t r = (int32_t)(keys[pairptr[q]] >> 32);
-  rows[q] = r;
+  span[2 * q] = rowptr[r]; span[2 * q + 1] = rowptr[r + 1];
   unsigned long long len = (unsigned long long)(rowptr[r + 1] - rowptr[r]);
   atomicAdd(&stat[0], len);
   atomicMax(&stat[1], len);
@@ -63,183 +73,218 @@ __global__ void __launch_bounds__(256) k_plan_rows(int64_t nrows, int64_t npairs
   if (q == nrows - 1) stat[3] = (unsigned long long)rowptr[r + 1];
 }
 
-// one thread per (pair, local column): position of the column inside the CSR row
-__global__ void __launch_bounds__(256) k_plan_desc(int64_t npairs, int nd, int64_t nlist, int ds, const uint64_t *__restrict__ keys,
-                                                  const int32_t *__restrict__ table, const int64_t *__restrict__ rowptr,
-                                                  const int32_t *__restrict__ colidx, uint8_t *__restrict__ desc, int *__restrict__ bad) {
-  int64_t t = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-  if (t >= npairs * nd) return;
-  int64_t pp = t / nd;
-  int j = (int)(t - pp * nd);
-  uint64_t key = keys[pp];
-  int32_t r = (int32_t)(key >> 32);
-  uint32_t p = (uint32_t)(key & 0xffffffffULL);
-  int i = (int)(p / (uint32_t)nlist);
-  uint32_t k = p - (uint32_t)i * (uint32_t)nlist;
-  int32_t col = table[(int64_t)k * nd + j];
-  int64_t rs = rowptr[r], lo = rs, hi = rowptr[r + 1] - 1;
-  while (lo < hi) {
-    int64_t mid = (lo + hi) >> 1;
-    if (colidx[mid] < col) lo = mid + 1; else hi = mid;
+// schedule record of a plan row (host -> device, symbolic phase only)
+struct RowSched { int32_t tile, start, lane, off; };
+
+// one thread per pair: its slot in the schedule, the positions of the nd local columns inside the CSR row
+__global__ void __launch_bounds__(128) k_plan_desc(int64_t npairs, int64_t nrows, int nd, int64_t nlist, int ds, const uint64_t *__restrict__ keys,
+                                                  const int64_t *__restrict__ pairptr, const RowSched *__restrict__ sched,
+                                                  const int64_t *__restrict__ tile_d0, const int64_t *__restrict__ tile_so,
+                                                  const int32_t *__restrict__ stepoffs, const int32_t *__restrict__ table,
+                                                  const int64_t *__restrict__ rowptr, const int32_t *__restrict__ colidx,
+                                                  uint8_t *__restrict__ desc, int *__restrict__ bad) {
+  const int64_t pp = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (pp >= npairs) return;
+  int64_t lo = 0, hi = nrows;                                   // plan row of the pair: last q with pairptr[q] <= pp
+  while (hi - lo > 1) {
+    const int64_t mid = (lo + hi) >> 1;
+    if (pairptr[mid] <= pp) lo = mid; else hi = mid;
   }
-  int64_t pos = lo - rs;
-  if (hi < rs || colidx[lo] != col) { atomicOr(bad, 1); pos = 0; }
-  if (pos >= MAXROW) { atomicOr(bad, 2); pos = 0; }
-  uint8_t *d = desc + pp * ds;
-  if (j == 0) { *reinterpret_cast<int32_t *>(d) = (int32_t)k; d[4] = (uint8_t)i; }
-  d[5 + j] = (uint8_t)pos;
+  const int64_t q = lo;
+  const RowSched rs = sched[q];
+  const int step = rs.start + (int)(pp - pairptr[q]);
+  const int64_t slot = tile_d0[rs.tile] + stepoffs[tile_so[rs.tile] + step] + rs.lane;
+  const uint64_t key = keys[pp];
+  const int32_t r = (int32_t)(key >> 32);
+  const uint32_t p = (uint32_t)(key & 0xffffffffULL);
+  const int i = (int)(p / (uint32_t)nlist);
+  const uint32_t k = p - (uint32_t)i * (uint32_t)nlist;
+  uint8_t *d = desc + slot * ds;
+  *reinterpret_cast<uint32_t *>(d) = k | ((uint32_t)i << DESC_KBITS);
+  *reinterpret_cast<uint16_t *>(d + 4) = (uint16_t)rs.off;
+  const int64_t rs0 = rowptr[r], re = rowptr[r + 1];
+  for (int j = 0; j < nd; j++) {
+    const int32_t col = table[(int64_t)k * nd + j];
+    int64_t a = rs0, b = re - 1;
+    while (a < b) {
+      const int64_t mid = (a + b) >> 1;
+      if (colidx[mid] < col) a = mid + 1; else b = mid;
+    }
+    int64_t pos = a - rs0;
+    if (b < rs0 || colidx[a] != col) { atomicOr(bad, 1); pos = 0; }
+    if (pos >= MAXROW) { atomicOr(bad, 2); pos = 0; }
+    d[6 + j] = (uint8_t)pos;
+  }
 }
 
-__global__ void __launch_bounds__(256) k_row_spans(int64_t nrows, const int32_t *__restrict__ rows, const int64_t *__restrict__ rowptr,
-                                                  int64_t *__restrict__ span) {
-  int64_t q = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-  if (q >= nrows) return;
-  const int32_t r = rows[q];
-  span[2 * q] = rowptr[r]; span[2 * q + 1] = rowptr[r + 1];
-}
-
-// processing order of the tiles: by the list index of the first contributing element, so that the vertex-row and edge-row
-// tiles of one mesh region run at about the same time (their geometry factors are then L2 hits); empty tiles sort last
-__global__ void __launch_bounds__(256) k_tile_keys(int64_t ntiles, const int32_t *__restrict__ tile_q, const int64_t *__restrict__ pairptr,
-                                                  const uint8_t *__restrict__ desc, int ds, uint32_t *__restrict__ keys, int32_t *__restrict__ ids,
-                                                  unsigned long long *__restrict__ nonempty) {
+// processing order of the tiles: by the list index of the first pair of the tile, so that the vertex-row and edge-row tiles of
+// one mesh region run at about the same time (their geometry records are then L2 hits)
+__global__ void __launch_bounds__(256) k_tile_keys(int64_t ntiles, const TileHdr *__restrict__ tiles, const uint8_t *__restrict__ desc, int ds,
+                                                  uint32_t *__restrict__ keys, int32_t *__restrict__ ids) {
   int64_t c = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (c >= ntiles) return;
-  int q0 = tile_q[c], q1 = tile_q[c + 1];
   ids[c] = (int32_t)c;
-  if (q0 == q1) { keys[c] = 0xffffffffu; return; }
-  keys[c] = (uint32_t)*reinterpret_cast<const int32_t *>(desc + pairptr[q0] * ds);
-  atomicAdd(nonempty, 1ULL);
+  keys[c] = *reinterpret_cast<const uint32_t *>(desc + tiles[c].d0 * ds) & DESC_KMASK;
+}
+__global__ void __launch_bounds__(256) k_tile_permute(int64_t ntiles, const int32_t *__restrict__ order, const TileHdr *__restrict__ in,
+                                                     TileHdr *__restrict__ out) {
+  int64_t c = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (c >= ntiles) return;
+  out[c] = in[order[c]];
 }
 
-// per tile, in processing order: CSR span and the row range of each lane -- the tile's pairs are cut into 32 equal parts
-// and every cut is moved to the next row boundary
-__global__ void __launch_bounds__(256) k_tile_tables(int64_t nact, const int32_t *__restrict__ order, const int32_t *__restrict__ tile_q,
-                                                    const int32_t *__restrict__ rows, const int64_t *__restrict__ rowptr,
-                                                    const int64_t *__restrict__ pairptr, TileInfo *__restrict__ info, int32_t *__restrict__ split) {
-  int64_t t = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-  if (t >= nact * 33) return;
-  const int64_t tt = t / 33;
-  const int k = (int)(t - tt * 33);
-  const int c = order[tt];
-  const int q0 = tile_q[c], q1 = tile_q[c + 1];
-  if (k == 32) {
-    TileInfo ti;
-    ti.z0 = rowptr[rows[q0]];
-    ti.zlen = (int32_t)(rowptr[rows[q1 - 1] + 1] - ti.z0);
-    ti.pad = 0;
-    info[tt] = ti;
-    split[t] = q1;
-    return;
-  }
-  const int64_t pa = pairptr[q0], pb = pairptr[q1];
-  const int64_t target = pa + ((pb - pa) * k) / 32;
-  int lo = q0, hi = q1;
-  while (lo < hi) {
-    int mid = (lo + hi) >> 1;
-    if (pairptr[mid] < target) lo = mid + 1; else hi = mid;
-  }
-  split[t] = lo;
+// slot of every (list entry, local row) pair -- what a producer of packed block rows needs (ngsx_rowplan_rowslots)
+__global__ void __launch_bounds__(256) k_rowslots(int64_t nslots, int nd, int ds, const uint8_t *__restrict__ desc, int32_t *__restrict__ rowslot) {
+  int64_t s = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (s >= nslots) return;
+  const uint32_t w = *reinterpret_cast<const uint32_t *>(desc + s * ds);
+  rowslot[(int64_t)(w & DESC_KMASK) * nd + (w >> DESC_KBITS)] = (int32_t)s;
 }
 
-// byte 5 + j of a descriptor = position of local column j in the row
+// ---- moments of the reference rule ----------------------------------------------------------------------------------
+bool rule_moments(int dim, int order, RuleMom *out) {
+  if (order < 0) order = 0;
+  const int maxo = dim == 2 ? NGSX_RULE_TRIG_MAXORDER : NGSX_RULE_TET_MAXORDER;
+  if ((dim != 2 && dim != 3) || order > maxo) return false;
+  const int *offs = dim == 2 ? NGSX_RULE_TRIG_OFFS : NGSX_RULE_TET_OFFS;
+  const double (*data)[4] = dim == 2 ? NGSX_RULE_TRIG_DATA : NGSX_RULE_TET_DATA;
+  const int nv = dim + 1;
+  double m1[4] = {0, 0, 0, 0}, m2[4][4] = {}, m3[4][4][4] = {}, m4[4][4][4][4] = {};
+  double m0 = 0.0;
+  for (int q = offs[order]; q < offs[order + 1]; q++) {
+    double l[4] = {data[q][0], data[q][1], dim == 3 ? data[q][2] : 0.0, 0.0};
+    double last = 1.0;
+    for (int k = 0; k < dim; k++) last -= l[k];
+    l[dim] = last;
+    const double w = data[q][3];
+    m0 += w;
+    for (int a = 0; a < nv; a++) {
+      m1[a] += w * l[a];
+      for (int b = 0; b < nv; b++) {
+        m2[a][b] += w * l[a] * l[b];
+        for (int c = 0; c < nv; c++) {
+          m3[a][b][c] += w * l[a] * l[b] * l[c];
+          for (int d = 0; d < nv; d++) m4[a][b][c][d] += w * l[a] * l[b] * l[c] * l[d];
+        }
+      }
+    }
+  }
+  RuleMom M{};
+  M.m0 = m0; M.m1 = m1[0]; M.m2s = m2[0][0]; M.m2d = m2[0][1]; M.m3aab = m3[0][0][1]; M.m3abc = m3[0][1][2];
+  M.m4aabb = m4[0][0][1][1]; M.m4aabc = m4[0][0][1][2]; M.m4abcd = dim == 3 ? m4[0][1][2][3] : 0.0;
+  const double tol = 1e-13 * fabs(m0);
+  bool sym = true;
+  auto chk = [&](double v, double ref) { if (fabs(v - ref) > tol) sym = false; };
+  for (int a = 0; a < nv; a++) {
+    chk(m1[a], M.m1);
+    for (int b = 0; b < nv; b++) {
+      chk(m2[a][b], a == b ? M.m2s : M.m2d);
+      for (int c = 0; c < nv; c++) {
+        const int distinct3 = (a != b) + (a != c) + (b != c);          // 0: aaa, 2: aab, 3: abc
+        if (distinct3 == 2) chk(m3[a][b][c], M.m3aab);
+        if (distinct3 == 3) chk(m3[a][b][c], M.m3abc);
+        for (int d = 0; d < nv; d++) {
+          int v[4] = {a, b, c, d};
+          std::sort(v, v + 4);
+          const bool aabb = v[0] == v[1] && v[2] == v[3] && v[1] != v[2];
+          const bool allx = v[0] != v[1] && v[1] != v[2] && v[2] != v[3];
+          const bool aabc = !aabb && !allx && ((v[0] == v[1]) + (v[1] == v[2]) + (v[2] == v[3]) == 1);
+          if (aabb) chk(m4[a][b][c][d], M.m4aabb);
+          if (aabc) chk(m4[a][b][c][d], M.m4aabc);
+          if (allx) chk(m4[a][b][c][d], M.m4abcd);
+        }
+      }
+    }
+  }
+  *out = M;
+  return sym;
+}
+
+// ---- the row kernel -------------------------------------------------------------------------------------------------
+struct RowArgs {
+  int64_t ntiles;
+  const TileHdr *tiles;
+  const uint4 *desc;
+  const double *G;
+  const double *cutmats;
+  double *vals;
+  int accumulate;
+  // rule constants of the closed forms (row_vertex / row_edge)
+  double m0, m2s, m2d, hm1, q3aab, q3abc, qm2d, qdm, q4[3];
+};
+
 template <int J> __device__ __forceinline__ int desc_pos(const uint4 &d) {
-  constexpr int b = 5 + J, w = b >> 2, sh = (b & 3) * 8;
+  constexpr int b = 6 + J, w = b >> 2, sh = (b & 3) * 8;
   const uint32_t x = w == 1 ? d.y : (w == 2 ? d.z : d.w);
   return (int)((x >> sh) & 0xffu);
 }
-
-// positions of the nd local columns (compile-time byte extraction)
 template <int ND, int J> __device__ __forceinline__ void desc_positions(const uint4 &d, int *pos) {
   if constexpr (J < ND) { pos[J] = desc_pos<J>(d); desc_positions<ND, J + 1>(d, pos); }
 }
 
-// 32-byte global load (sm_100: LDG.E.256): one L1 tag lookup per half geometry record instead of two
+// 32-byte global load (sm_100: LDG.E.256)
 __device__ __forceinline__ void ldg256(const double *p, double *o) {
   asm volatile("ld.global.nc.v4.f64 {%0, %1, %2, %3}, [%4];" : "=d"(o[0]), "=d"(o[1]), "=d"(o[2]), "=d"(o[3]) : "l"(p));
 }
 
-// Row i of a constant-rule element matrix from the element's geometry factors, by sum factorisation.
-//   A_ij = |J| c_s sum_r w_r (grad phi_i)^T (J^-1 J^-T) (grad phi_j) + |J| c_m sum_r w_r phi_i phi_j
-// The reference gradients of P1/P2 shapes are affine in the reference coordinates, d_a phi_i = sum_m c_iam X_m, so with the
-// rule's moments folded into cM[i][a][n] (k_ref_tables):  w[b][n] = sum_a Ghat_ab cM[i][a][n]  (36 FMAs in 3D) and
-//   vertex j:      A_ij = w[.][0] . grad lam_j
-//   edge (a, b):   A_ij = -1/2 (Q[a][b] + Q[b][a]),  Q[a][k] = grad lam_a . W(., lam_k),  W(b, lam_k) = coefficient of lam_k in w[b][.]
-// Same quadrature as the reference's static rule, re-associated; 12 + nd doubles of table per pair instead of 7 nd.
+// Row i of the constant-rule element matrix  A_ij = sum_r w_r (grad phi_i)^T Ghat (grad phi_j) + gm sum_r w_r phi_i phi_j,
+// Ghat = |J| c_s J^-1 J^-T, gm = |J| c_m, for a permutation-symmetric rule.  With K[a][b] = grad(lam_a) Ghat grad(lam_b):
+//   vertex i, vertex c:       m0 K[i][c] + gm M2(i,c)                         M2 = m2s (same vertex) / m2d
+//   vertex i, edge (c,d):    -1/2 m1 (K[i][c] + K[i][d]) - 1/2 gm M3(i,c,d)   M3 = m3aab (i on the edge) / m3abc
+//   edge (a,b), vertex c:    -1/2 m1 (K[a][c] + K[b][c]) - 1/2 gm M3(c,a,b)
+//   edge (a,b), edge (c,d):   1/4 [K[b][d] M2(a,c) + K[b][c] M2(a,d) + K[a][d] M2(b,c) + K[a][c] M2(b,d)] + 1/4 gm M4(a,b,c,d)
+// (phi_edge = -1/2 lam_a lam_b, NGS/fem/recursive_pol.hpp:1372).  ka = K[a][0..DIM-1] is what k_geom stores per local vertex;
+// K[a][DIM] = -sum.  Same quadrature as the reference's static rule, re-associated.
 template <int DIM, int ORDER>
-__device__ __forceinline__ void row_values(const double *g, const double *cmi, const double *tm, double *v) {
-  constexpr int ND = H1<DIM, ORDER>::ND, NEDGE = H1<DIM, ORDER>::NEDGE;
-  double Gh[DIM][DIM];
-  {
-    int pr = 0;
+__device__ __forceinline__ void row_vertex(const RowArgs &A, int i, const double *ga, double *v) {
+  constexpr int NEDGE = H1<DIM, ORDER>::NEDGE;
+  double kv[DIM + 1];
+  double s = 0.0;
 #pragma unroll
-    for (int a = 0; a < DIM; a++)
+  for (int c = 0; c < DIM; c++) { kv[c] = ga[c]; s += ga[c]; }
+  kv[DIM] = -s;
+  const double gm = ga[3];
+  const double gs = gm * A.m2s, gd = gm * A.m2d;
 #pragma unroll
-      for (int b = a; b < DIM; b++) { Gh[a][b] = g[pr]; Gh[b][a] = g[pr]; pr++; }
-  }
-  double c[DIM][DIM + 1];
-  if constexpr (DIM == 3) {
-#pragma unroll
-    for (int t = 0; t < 6; t++) {
-      const double2 x = *reinterpret_cast<const double2 *>(cmi + 2 * t);
-      c[(2 * t) / 4][(2 * t) % 4] = x.x; c[(2 * t + 1) / 4][(2 * t + 1) % 4] = x.y;
-    }
-  } else {
-#pragma unroll
-    for (int t = 0; t < 3; t++) {
-      const double2 x = *reinterpret_cast<const double2 *>(cmi + 2 * t);
-      c[(2 * t) / 3][(2 * t) % 3] = x.x; c[(2 * t + 1) / 3][(2 * t + 1) % 3] = x.y;
-    }
-  }
-  double w[DIM][DIM + 1];
-#pragma unroll
-  for (int b = 0; b < DIM; b++)
-#pragma unroll
-    for (int n = 0; n <= DIM; n++) {
-      double s = Gh[0][b] * c[0][n];
-#pragma unroll
-      for (int a = 1; a < DIM; a++) s = fma(Gh[a][b], c[a][n], s);
-      w[b][n] = s;
-    }
-  // vertex functions: grad lam_j = e_j (j < DIM), -(1,..,1) (j = DIM)
-  double dsum = 0.0;
-#pragma unroll
-  for (int j = 0; j < DIM; j++) { v[j] = w[j][0]; dsum += w[j][0]; }
-  v[DIM] = -dsum;
+  for (int c = 0; c <= DIM; c++) v[c] = fma(A.m0, kv[c], i == c ? gs : gd);
   if constexpr (ORDER == 2) {
-    double Q[DIM + 1][DIM + 1];
+    const double gin = gm * A.q3aab, gout = gm * A.q3abc;
 #pragma unroll
-    for (int b = 0; b < DIM; b++) {
-      double last = w[b][0];
-#pragma unroll
-      for (int k = 0; k < DIM; k++) { Q[b][k] = w[b][k + 1]; last -= w[b][k + 1]; }
-      Q[b][DIM] = last;
-    }
-#pragma unroll
-    for (int k = 0; k <= DIM; k++) {
-      double z = Q[0][k];
-#pragma unroll
-      for (int b = 1; b < DIM; b++) z += Q[b][k];
-      Q[DIM][k] = -z;
-    }
-#pragma unroll
-    for (int ed = 0; ed < NEDGE; ed++) {
-      int a, b;
-      edge_vertices<DIM>(ed, a, b);
-      v[DIM + 1 + ed] = -0.5 * (Q[a][b] + Q[b][a]);
+    for (int e = 0; e < NEDGE; e++) {
+      int c, d;
+      edge_vertices<DIM>(e, c, d);
+      v[DIM + 1 + e] = fma(A.hm1, kv[c] + kv[d], (i == c || i == d) ? gin : gout);
     }
   }
-  // mass
-  const double gm = g[6];
-  if constexpr (ND % 2 == 0) {
+}
+
+template <int DIM>
+__device__ __forceinline__ void row_edge(const RowArgs &A, int a, int b, const double *ga, const double *gb, double *v) {
+  constexpr int NEDGE = H1<DIM, 2>::NEDGE;
+  double ka[DIM + 1], kb[DIM + 1], ks[DIM + 1];
+  double sa = 0.0, sb = 0.0;
 #pragma unroll
-    for (int j = 0; j < ND; j += 2) {
-      const double2 t = *reinterpret_cast<const double2 *>(tm + j);
-      v[j] = fma(gm, t.x, v[j]); v[j + 1] = fma(gm, t.y, v[j + 1]);
-    }
-  } else {
+  for (int c = 0; c < DIM; c++) { ka[c] = ga[c]; kb[c] = gb[c]; sa += ga[c]; sb += gb[c]; }
+  ka[DIM] = -sa; kb[DIM] = -sb;
 #pragma unroll
-    for (int j = 0; j < ND; j++) v[j] = fma(gm, tm[j], v[j]);
+  for (int c = 0; c <= DIM; c++) ks[c] = ka[c] + kb[c];
+  const double gm = ga[3];
+  const double gin = gm * A.q3aab, gout = gm * A.q3abc;
+#pragma unroll
+  for (int c = 0; c <= DIM; c++) v[c] = fma(A.hm1, ks[c], (c == a || c == b) ? gin : gout);
+  const double g0 = gm * A.q4[0], g1 = gm * A.q4[1], g2 = gm * A.q4[2];
+#pragma unroll
+  for (int e = 0; e < NEDGE; e++) {
+    int c, d;
+    edge_vertices<DIM>(e, c, d);
+    double corr = 0.0;
+    if (a == c) corr += kb[d];
+    if (a == d) corr += kb[c];
+    if (b == c) corr += ka[d];
+    if (b == d) corr += ka[c];
+    const int cnt = (a == c) + (a == d) + (b == c) + (b == d);
+    const double gq = cnt == 2 ? g2 : (cnt == 1 ? g1 : g0);
+    v[DIM + 1 + e] = fma(A.qm2d, ks[c] + ks[d], fma(A.qdm, corr, gq));
   }
 }
 
@@ -258,113 +303,90 @@ __device__ __forceinline__ void row_values_cut(const double *cm, double *v) {
   }
 }
 
-// ---- the row kernel ---------------------------------------------------------------------------------------------
-// WARP = one tile of consecutive CSR rows whose values (<= ACCW doubles) live in the warp's private shared-memory window:
-// initialised by the warp (zero, or the current values when accumulating), gathered, and streamed out once with coalesced
-// stores.  Warps never wait for each other (no CTA barrier after the table load).
-// LANE = one contiguous range of the tile's rows (pair-balanced split from the plan): the lane walks the (row, element)
-// pairs of its range in plan order; per pair it contracts the element's 7 geometry factors with row i of the reference
-// tables (nd entries, shared-memory vector loads) and adds them at their positions of the row.  No two lanes share a row
-// and the nd columns of one element are distinct, so the summation order of every CSR entry is the plan order: bitwise
-// reproducible, no atomics.  Descriptors are prefetched two pairs ahead, geometry factors one pair ahead, row records one
-// row ahead; the start-up loads of the next tile are issued before the current tile is streamed out.
-struct RowArgs {
-  int64_t ntiles;             // non-empty tiles, in processing order
-  const TileInfo *info;       // [ntiles]
-  const int32_t *split;       // [ntiles][33] first plan row of each lane's range
-  const RowRec *rowrec;
-  const uint4 *desc;
-  const double *G;
-  const double *cutmats;
-  const double *tab;
-  double *vals;
-  int accumulate;
-};
-
-// per-lane walk state over the pairs [pcur, plast) of the rows [q, qb)
-struct LaneState {
-  int q, qb, off;
-  uint32_t pcur, pend, plast;
-  RowRec recn;
-  uint4 d1, d2;
-  double g1[8];               // geometry record of pair pcur (g1[7] = code)
-};
-
-__device__ __forceinline__ void lane_start(const RowArgs &A, int64_t tt, int lane, LaneState &S) {
-  const int32_t *split = A.split + tt * 33;
-  S.q = __ldg(split + lane); S.qb = __ldg(split + lane + 1);
-  S.pcur = S.pend = S.plast = 0; S.off = 0;
-  S.recn = RowRec{0, 0, 0};
-  S.d1 = S.d2 = make_uint4(0u, 0u, 0u, 0u);
-#pragma unroll
-  for (int m = 0; m < 8; m++) S.g1[m] = 0.0;
-  if (S.q < S.qb) {
-    const RowRec rec = ld_rowrec(A.rowrec + S.q), recl = ld_rowrec(A.rowrec + S.qb - 1);
-    S.pcur = rec.p0; S.pend = rec.p0 + rec.np; S.off = rec.off; S.plast = recl.p0 + recl.np;
-    S.recn = (S.q + 1 < S.qb) ? ld_rowrec(A.rowrec + S.q + 1) : rec;
-    S.d1 = __ldg(A.desc + S.pcur);
-    if (S.pcur + 1 < S.plast) S.d2 = __ldg(A.desc + S.pcur + 1);
-    const double *Gk = A.G + (int64_t)(int)S.d1.x * GSTRIDE;
-    ldg256(Gk, S.g1); ldg256(Gk + 4, S.g1 + 4);
+// geometry record(s) of a pair: vertex row i -> record i; edge row (a, b) -> records a and b (the same 128-byte line)
+template <int DIM, int ORDER>
+__device__ __forceinline__ void load_geo(const RowArgs &A, uint32_t w0, double *ga, double *gb) {
+  constexpr int GS = (DIM + 1) * 4;
+  const int i = (int)(w0 >> DESC_KBITS);
+  const double *Gk = A.G + (int64_t)(w0 & DESC_KMASK) * GS;
+  if (ORDER == 1 || i <= DIM) {
+    ldg256(Gk + 4 * i, ga);
+  } else {
+    int a, b;
+    edge_vertices<DIM>(i - (DIM + 1), a, b);
+    ldg256(Gk + 4 * a, ga);
+    ldg256(Gk + 4 * b, gb);
   }
 }
 
+// WARP = one tile of consecutive CSR rows whose values (<= ACCW doubles) live in the warp's private shared-memory window:
+// initialised by the warp (zero, or the current values when accumulating), gathered, and streamed out once with coalesced
+// stores.  Warps never wait for each other.  LANE = the rows the schedule dealt to it: per step one (row, element) pair --
+// descriptor (prefetched two steps ahead, coalesced), geometry record(s) (one step ahead), closed-form row, nd window adds.
+// No two lanes share a row and the nd columns of one element are distinct, so every CSR entry is summed in plan order.
 template <int DIM, int ORDER>
 __global__ void __launch_bounds__(RW * 32, NGSX_MINBLOCKS) k_rows(RowArgs A) {
-  constexpr int ND = H1<DIM, ORDER>::ND, NE = ND * ND, CS = RefTab<DIM>::CS, CMO = RefTab<DIM>::cm_offset(NE), NTAB = CMO + ND * CS;
+  constexpr int ND = H1<DIM, ORDER>::ND, NE = ND * ND;
   extern __shared__ __align__(16) double smem_rows[];
-  double *tab = smem_rows;                                        // mass table [ND][ND], then cM [ND][CS]
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  double *acc = smem_rows + NTAB + warp * ACCW;                    // this warp's window
-  for (int t = threadIdx.x; t < NTAB; t += blockDim.x) tab[t] = A.tab[t];
-  __syncthreads();
+  double *acc = smem_rows + warp * ACCW;
   const int64_t nwarps = (int64_t)gridDim.x * RW;
-  int64_t tt = (int64_t)blockIdx.x * RW + warp;
-  LaneState S;
-  TileInfo ti{0, 0, 0};
-  if (tt < A.ntiles) { ti = A.info[tt]; lane_start(A, tt, lane, S); }
-  while (tt < A.ntiles) {
-    const int64_t z0 = ti.z0;
-    const int zlen = ti.zlen;
+  const uint4 null4 = make_uint4(0xffffffffu, 0u, 0u, 0u);
+  for (int64_t tt = (int64_t)blockIdx.x * RW + warp; tt < A.ntiles; tt += nwarps) {
+    const TileHdr *H = A.tiles + tt;
+    const int64_t z0 = __ldg(&H->z0);
+    const int zlen = __ldg(&H->zlen), nsteps = __ldg(&H->nsteps);
+    const int myload = __ldg(&H->load[lane]);
+    int64_t base2 = __ldg(&H->d0);
+    // prime the pipeline: descriptors of steps 0 and 1, geometry of step 0
+    uint4 dcur = null4, dnext = null4;
+    if (0 < myload) dcur = __ldg(A.desc + base2 + lane);
+    base2 += __popc(__ballot_sync(0xffffffffu, 0 < myload));
+    if (1 < myload) dnext = __ldg(A.desc + base2 + lane);
+    base2 += __popc(__ballot_sync(0xffffffffu, 1 < myload));
+    double ga[4] = {0.0, 0.0, 0.0, 0.0}, gb[4] = {0.0, 0.0, 0.0, 0.0};
+    if (0 < myload) load_geo<DIM, ORDER>(A, dcur.x, ga, gb);
     if (A.accumulate) for (int t = lane; t < zlen; t += 32) acc[t] = A.vals[z0 + t];
     else for (int t = lane; t < zlen; t += 32) acc[t] = 0.0;
     __syncwarp();
-    while (S.pcur < S.plast) {
-      const uint4 d = S.d1;
-      double g[8];
+    for (int s = 0; s < nsteps; s++) {
+      const uint4 d = dcur;
+      double a4[4], b4[4];
 #pragma unroll
-      for (int m = 0; m < 8; m++) g[m] = S.g1[m];
-      const long long code = __double_as_longlong(g[7]);
-      if (S.pcur == S.pend) {                      // first pair of the next row
-        S.q++;
-        S.pend = S.recn.p0 + S.recn.np; S.off = S.recn.off;
-        if (S.q + 1 < S.qb) S.recn = ld_rowrec(A.rowrec + S.q + 1);
-      }
-      if (S.pcur + 1 < S.plast) {                  // advance the prefetch pipeline
-        S.d1 = S.d2;
-        const double *Gk = A.G + (int64_t)(int)S.d1.x * GSTRIDE;
-        ldg256(Gk, S.g1); ldg256(Gk + 4, S.g1 + 4);
-        if (S.pcur + 2 < S.plast) S.d2 = __ldg(A.desc + S.pcur + 2);
-      }
-      if (code >= 0) {
-        const int i = (int)(d.y & 0xffu);
-        double v[ND], a[ND];
-        int pos[ND];
-        desc_positions<ND, 0>(d, pos);
-        double *accrow = acc + S.off;
-        // the nd columns of an element are distinct: read all, add, write all (no serialised read-modify-write chain)
+      for (int m = 0; m < 4; m++) { a4[m] = ga[m]; b4[m] = gb[m]; }
+      dcur = dnext;
+      if (s + 2 < myload) dnext = __ldg(A.desc + base2 + lane);
+      base2 += __popc(__ballot_sync(0xffffffffu, s + 2 < myload));
+      if (s + 1 < myload) load_geo<DIM, ORDER>(A, dcur.x, ga, gb);
+      if (s < myload) {
+        const int i = (int)(d.x >> DESC_KBITS);
+        const unsigned long long cb = (unsigned long long)__double_as_longlong(a4[3]);
+        const bool coded = a4[3] != a4[3];
+        const unsigned payload = (unsigned)(cb & 0xffffffffULL);
+        if (!coded || payload != 0u) {
+          double v[ND], w[ND];
+          int pos[ND];
+          desc_positions<ND, 0>(d, pos);
+          double *accrow = acc + (d.y & 0xffffu);
+          // the nd columns of an element are distinct: read all, add, write all (no serialised read-modify-write chain)
 #pragma unroll
-        for (int j = 0; j < ND; j++) a[j] = accrow[pos[j]];
-        if (code > 0) row_values_cut<ND>(A.cutmats + (code - 1) * NE + i * ND, v);
-        else row_values<DIM, ORDER>(g, tab + CMO + i * CS, tab + i * ND, v);
+          for (int j = 0; j < ND; j++) w[j] = accrow[pos[j]];
+          if (coded) {
+            row_values_cut<ND>(A.cutmats + (int64_t)(payload - 1u) * NE + i * ND, v);
+          } else if (ORDER == 1 || i <= DIM) {
+            row_vertex<DIM, ORDER>(A, i, a4, v);
+          } else {
+            if constexpr (ORDER == 2) {
+              int ea, eb;
+              edge_vertices<DIM>(i - (DIM + 1), ea, eb);
+              row_edge<DIM>(A, ea, eb, a4, b4, v);
+            }
+          }
 #pragma unroll
-        for (int j = 0; j < ND; j++) accrow[pos[j]] = a[j] + v[j];
+          for (int j = 0; j < ND; j++) accrow[pos[j]] = w[j] + v[j];
+        }
       }
-      S.pcur++;
     }
-    // next tile: issue its start-up loads now, they fly while this tile is streamed out
-    tt += nwarps;
-    if (tt < A.ntiles) { ti = A.info[tt]; lane_start(A, tt, lane, S); }
     __syncwarp();
     for (int t = lane; t < zlen; t += 32) A.vals[z0 + t] = acc[t];
     __syncwarp();
@@ -373,8 +395,7 @@ __global__ void __launch_bounds__(RW * 32, NGSX_MINBLOCKS) k_rows(RowArgs A) {
 
 template <int DIM, int ORDER>
 static int launch_rows_t(const RowArgs &A, int sm_count, cudaStream_t st) {
-  constexpr int ND = H1<DIM, ORDER>::ND, NTAB = RefTab<DIM>::cm_offset(ND * ND) + ND * RefTab<DIM>::CS;
-  size_t smem = (size_t)(NTAB + RW * ACCW) * sizeof(double);
+  size_t smem = (size_t)RW * ACCW * sizeof(double);
   auto kern = k_rows<DIM, ORDER>;
   NGSX_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   int occ = 0;
@@ -387,26 +408,37 @@ static int launch_rows_t(const RowArgs &A, int sm_count, cudaStream_t st) {
   return NGSX_OK;
 }
 
-int rows_scratch(ngsx_rowplan *P, int npairtab) {
-  const int64_t ne2 = (int64_t)P->nd * P->nd;
-  if (!P->G) NGSX_CUDA(cudaMalloc(&P->G, std::max<int64_t>(1, P->nlist) * GSTRIDE * sizeof(double)));
-  if (!P->cutlist) NGSX_CUDA(cudaMalloc(&P->cutlist, std::max<int64_t>(1, P->nlist) * sizeof(int32_t)));
-  if (!P->cutcount) NGSX_CUDA(cudaMalloc(&P->cutcount, sizeof(int32_t)));
-  if (!P->cutmats) NGSX_CUDA(cudaMalloc(&P->cutmats, std::max<int64_t>(1, P->nlist) * ne2 * sizeof(double)));
-  if (!P->tab) NGSX_CUDA(cudaMalloc(&P->tab, (size_t)(npairtab + 1) * ne2 * sizeof(double)));
+int rows_reserve_cut(ngsx_rowplan *P, int64_t cap) {
+  cap = std::max<int64_t>(1, std::min<int64_t>(cap, std::max<int64_t>(1, P->nlist)));
+  if (cap <= P->cut_cap) return NGSX_OK;
+  if (P->cutmats) { NGSX_CUDA(cudaDeviceSynchronize()); cudaFree(P->cutmats); P->cutmats = nullptr; P->cut_cap = 0; }
+  NGSX_CUDA(cudaMalloc(&P->cutmats, (size_t)cap * P->nd * P->nd * sizeof(double)));
+  P->cut_cap = cap;
   return NGSX_OK;
 }
 
-int launch_rows(const ngsx_rowplan *P, int npairtab, int accumulate, double *vals, int sm_count, cudaStream_t st) {
+int rows_scratch(ngsx_rowplan *P, int dim) {
+  if (P->G && P->g_dim != dim) { NGSX_CUDA(cudaDeviceSynchronize()); cudaFree(P->G); P->G = nullptr; }
+  if (!P->G) { NGSX_CUDA(cudaMalloc(&P->G, std::max<int64_t>(1, P->nlist) * (dim + 1) * 4 * sizeof(double))); P->g_dim = dim; }
+  if (!P->cutlist) NGSX_CUDA(cudaMalloc(&P->cutlist, std::max<int64_t>(1, P->nlist) * sizeof(int32_t)));
+  if (!P->cutcount) NGSX_CUDA(cudaMalloc(&P->cutcount, sizeof(int32_t)));
+  return NGSX_OK;
+}
+
+int launch_rows(const ngsx_rowplan *P, int dim, const RuleMom &M, int accumulate, double *vals, int sm_count, cudaStream_t st) {
   if (P->nrows == 0) return NGSX_OK;
   if (P->ds != 16) { set_error("row gather: this plan was built for merged facet-patch dof lists (use ngsx_assemble_csr_rows_mats)"); return NGSX_ERR_ARG; }
-  RowArgs A{P->ntiles_active, P->tile_info, P->tile_split, P->rowrec, reinterpret_cast<const uint4 *>(P->desc), P->G, P->cutmats, P->tab,
-            vals, accumulate};
-  switch (P->nd * 10 + npairtab) {
-    case 33: return launch_rows_t<2, 1>(A, sm_count, st);
-    case 63: return launch_rows_t<2, 2>(A, sm_count, st);
-    case 46: return launch_rows_t<3, 1>(A, sm_count, st);
-    case 106: return launch_rows_t<3, 2>(A, sm_count, st);
+  RowArgs A{};
+  A.ntiles = P->ntiles; A.tiles = P->tiles; A.desc = reinterpret_cast<const uint4 *>(P->desc); A.G = P->G; A.cutmats = P->cutmats;
+  A.vals = vals; A.accumulate = accumulate;
+  A.m0 = M.m0; A.m2s = M.m2s; A.m2d = M.m2d; A.hm1 = -0.5 * M.m1; A.q3aab = -0.5 * M.m3aab; A.q3abc = -0.5 * M.m3abc;
+  A.qm2d = 0.25 * M.m2d; A.qdm = 0.25 * (M.m2s - M.m2d);
+  A.q4[0] = 0.25 * M.m4abcd; A.q4[1] = 0.25 * M.m4aabc; A.q4[2] = 0.25 * M.m4aabb;
+  switch (dim * 100 + P->nd) {
+    case 203: return launch_rows_t<2, 1>(A, sm_count, st);
+    case 206: return launch_rows_t<2, 2>(A, sm_count, st);
+    case 304: return launch_rows_t<3, 1>(A, sm_count, st);
+    case 310: return launch_rows_t<3, 2>(A, sm_count, st);
   }
   set_error("row gather: unsupported (dofs per element, dimension)");
   return NGSX_ERR_UNSUPPORTED;
@@ -421,8 +453,8 @@ extern "C" {
 int ngsx_rowplan_destroy(ngsx_rowplan *P) {
   if (!P) return NGSX_OK;
   cudaDeviceSynchronize();
-  cudaFree(P->rows); cudaFree(P->pairptr); cudaFree(P->desc); cudaFree(P->rowrec); cudaFree(P->tile_q); cudaFree(P->tile_info); cudaFree(P->tile_split);
-  cudaFree(P->G); cudaFree(P->cutlist); cudaFree(P->cutcount); cudaFree(P->cutmats); cudaFree(P->tab);
+  cudaFree(P->tiles); cudaFree(P->desc); cudaFree(P->rowslot);
+  cudaFree(P->G); cudaFree(P->cutlist); cudaFree(P->cutcount); cudaFree(P->cutmats);
   delete P;
   return NGSX_OK;
 }
@@ -431,6 +463,39 @@ int ngsx_rowplan_info(const ngsx_rowplan *P, int64_t *h_info) {
   NGSX_REQUIRE(P && h_info, "rowplan_info: bad arguments");
   h_info[0] = P->nrows; h_info[1] = P->npairs; h_info[2] = P->nnz_covered; h_info[3] = P->max_row;
   h_info[4] = P->nnz_lo; h_info[5] = P->nnz_hi;
+  return NGSX_OK;
+}
+
+int ngsx_rowplan_cut_usage(ngsx_rowplan *P, int64_t *h_count, int64_t *h_cap, void *stream) {
+  NGSX_REQUIRE(P && h_count && h_cap, "rowplan_cut_usage: bad arguments");
+  *h_count = 0; *h_cap = P->cut_cap;
+  if (!P->cutcount) return NGSX_OK;
+  int32_t c = 0;
+  NGSX_CUDA(cudaMemcpyAsync(&c, P->cutcount, sizeof c, cudaMemcpyDeviceToHost, as_stream(stream)));
+  NGSX_CUDA(cudaStreamSynchronize(as_stream(stream)));
+  *h_count = c;
+  return NGSX_OK;
+}
+
+int ngsx_rowplan_reserve_cut(ngsx_rowplan *P, int64_t capacity) {
+  NGSX_REQUIRE(P && capacity >= 0, "rowplan_reserve_cut: bad arguments");
+  return rows_reserve_cut(P, capacity);
+}
+
+int ngsx_rowplan_rowslots(ngsx_rowplan *P, const int32_t **d_rowslot, int64_t *h_nslots, void *stream) {
+  NGSX_REQUIRE(P && d_rowslot && h_nslots, "rowplan_rowslots: bad arguments");
+  cudaStream_t st = as_stream(stream);
+  if (!P->rowslot) {
+    const int64_t n = std::max<int64_t>(1, P->nlist * P->nd);
+    NGSX_CUDA(cudaMalloc(&P->rowslot, n * sizeof(int32_t)));
+    NGSX_CUDA(cudaMemsetAsync(P->rowslot, 0xff, n * sizeof(int32_t), st));
+    if (P->nslots > 0) {
+      k_rowslots<<<(unsigned)((P->nslots + 255) / 256), 256, 0, st>>>(P->nslots, P->nd, P->ds, P->desc, P->rowslot);
+      NGSX_LAUNCH_CHECK();
+    }
+    NGSX_CUDA(cudaStreamSynchronize(st));
+  }
+  *d_rowslot = P->rowslot; *h_nslots = P->nslots;
   return NGSX_OK;
 }
 
@@ -450,14 +515,15 @@ int ngsx_rowplan_create_owned(int64_t nlist, int32_t nd, const int32_t *table, i
 
 static int rowplan_create(int64_t nlist, int32_t nd, const int32_t *table, int64_t ndof, const int64_t *rowptr, const int32_t *colidx,
                           int64_t row_lo, int64_t row_hi, const int32_t *row_owner, int32_t me, ngsx_rowplan **out, void *stream) {
-  NGSX_REQUIRE(out && nlist >= 0 && nd > 0 && nd <= 27 && ndof >= 0 && ndof < (1LL << 31) && rowptr, "rowplan_create: bad arguments");
+  NGSX_REQUIRE(out && nlist >= 0 && nd > 0 && nd <= 26 && ndof >= 0 && ndof < (1LL << 31) && rowptr, "rowplan_create: bad arguments");
   NGSX_REQUIRE(nlist == 0 || (table && colidx), "rowplan_create: table / colidx are NULL");
-  NGSX_REQUIRE(nlist * nd < (1LL << 32), "rowplan_create: more than 2^32 (element, dof) pairs");
+  NGSX_REQUIRE(nlist * nd < (1LL << 31), "rowplan_create: more than 2^31 (element, dof) pairs");
+  NGSX_REQUIRE(nlist <= (int64_t)DESC_KMASK, "rowplan_create: more than 2^27 - 1 list entries in one plan");
   cudaStream_t st = as_stream(stream);
   if (row_hi < 0 || row_hi > ndof) row_hi = ndof;
   if (row_lo < 0) row_lo = 0;
   ngsx_rowplan *P = new ngsx_rowplan();
-  P->nlist = nlist; P->nd = nd; P->ndof = ndof; P->ds = nd <= 11 ? 16 : 32; P->rowptr = rowptr;
+  P->nlist = nlist; P->nd = nd; P->ndof = ndof; P->ds = nd <= 10 ? 16 : 32; P->rowptr = rowptr;
   *out = P;
   const int64_t nall = nlist * nd;
   if (nall == 0 || row_hi <= row_lo) return NGSX_OK;
@@ -468,10 +534,20 @@ static int rowplan_create(int64_t nlist, int32_t nd, const int32_t *table, int64
   int64_t *d_scalar = nullptr;          // [0] valid pairs, [1] rows
   unsigned long long *d_stat = nullptr;
   int *d_bad = nullptr;
-  auto cleanup = [&]() { cudaFree(keys); cudaFree(alt); cudaFree(flags); cudaFree(tmp); cudaFree(d_scalar); cudaFree(d_stat); cudaFree(d_bad); };
+  int64_t *d_pairptr = nullptr, *d_span = nullptr, *d_tile_d0 = nullptr, *d_tile_so = nullptr;
+  RowSched *d_sched = nullptr;
+  int32_t *d_stepoffs = nullptr, *d_order = nullptr, *d_ids = nullptr;
+  uint32_t *d_ck = nullptr, *d_ck2 = nullptr;
+  TileHdr *d_tiles_nat = nullptr;
+  auto cleanup = [&]() {
+    cudaFree(keys); cudaFree(alt); cudaFree(flags); cudaFree(tmp); cudaFree(d_scalar); cudaFree(d_stat); cudaFree(d_bad);
+    cudaFree(d_pairptr); cudaFree(d_span); cudaFree(d_tile_d0); cudaFree(d_tile_so); cudaFree(d_sched); cudaFree(d_stepoffs);
+    cudaFree(d_order); cudaFree(d_ids); cudaFree(d_ck); cudaFree(d_ck2); cudaFree(d_tiles_nat);
+  };
 #define PLAN_CUDA(call)                                                                                         \
   do { cudaError_t e__ = (call); if (e__ != cudaSuccess) { set_error(std::string(#call) + ": " + cudaGetErrorString(e__)); \
        cleanup(); ngsx_rowplan_destroy(P); *out = nullptr; return NGSX_ERR_CUDA; } } while (0)
+#define PLAN_FAIL(status, msg) do { set_error(msg); cleanup(); ngsx_rowplan_destroy(P); *out = nullptr; return status; } while (0)
 
   PLAN_CUDA(cudaMalloc(&keys, nall * sizeof(uint64_t)));
   PLAN_CUDA(cudaMalloc(&alt, nall * sizeof(uint64_t)));
@@ -492,123 +568,147 @@ static int rowplan_create(int64_t nlist, int32_t nd, const int32_t *table, int64
   PLAN_CUDA(cudaMemcpyAsync(&npairs, d_scalar, sizeof(int64_t), cudaMemcpyDeviceToHost, st));
   PLAN_CUDA(cudaStreamSynchronize(st));
   g_launches.fetch_add(4);
-  P->npairs = npairs;
+  P->npairs = npairs; P->nslots = npairs;
   if (npairs == 0) { cleanup(); return NGSX_OK; }
 
   PLAN_CUDA(cudaMalloc(&flags, npairs));
   k_head_flags<<<(unsigned)((npairs + 255) / 256), 256, 0, st>>>(npairs, sorted, flags);
-  // pair offsets of the row heads: at most min(npairs, rows in range) of them
-  int64_t cap_rows = std::min<int64_t>(npairs, row_hi - row_lo);
-  PLAN_CUDA(cudaMalloc(&P->pairptr, (cap_rows + 1) * sizeof(int64_t)));
+  const int64_t cap_rows = std::min<int64_t>(npairs, row_hi - row_lo);
+  PLAN_CUDA(cudaMalloc(&d_pairptr, (cap_rows + 1) * sizeof(int64_t)));
   cudaFree(tmp); tmp = nullptr; tmp_bytes = 0;
   thrust::counting_iterator<int64_t> counting(0);
-  PLAN_CUDA(cub::DeviceSelect::Flagged(nullptr, tmp_bytes, counting, flags, P->pairptr, d_scalar + 1, npairs, st));
+  PLAN_CUDA(cub::DeviceSelect::Flagged(nullptr, tmp_bytes, counting, flags, d_pairptr, d_scalar + 1, npairs, st));
   PLAN_CUDA(cudaMalloc(&tmp, tmp_bytes));
-  PLAN_CUDA(cub::DeviceSelect::Flagged(tmp, tmp_bytes, counting, flags, P->pairptr, d_scalar + 1, npairs, st));
+  PLAN_CUDA(cub::DeviceSelect::Flagged(tmp, tmp_bytes, counting, flags, d_pairptr, d_scalar + 1, npairs, st));
   int64_t nrows = 0;
   PLAN_CUDA(cudaMemcpyAsync(&nrows, d_scalar + 1, sizeof(int64_t), cudaMemcpyDeviceToHost, st));
   PLAN_CUDA(cudaStreamSynchronize(st));
   g_launches.fetch_add(3);
   P->nrows = nrows;
-  PLAN_CUDA(cudaMalloc(&P->rows, nrows * sizeof(int32_t)));
-  PLAN_CUDA(cudaMalloc(&P->desc, (size_t)npairs * P->ds));
-  PLAN_CUDA(cudaMemsetAsync(P->desc, 0, (size_t)npairs * P->ds, st));
-  k_plan_rows<<<(unsigned)((nrows + 255) / 256), 256, 0, st>>>(nrows, npairs, sorted, P->pairptr, rowptr, P->rows, d_stat);
-  k_plan_desc<<<(unsigned)((npairs * nd + 255) / 256), 256, 0, st>>>(npairs, nd, nlist, P->ds, sorted, table, rowptr, colidx, P->desc, d_bad);
-  g_launches.fetch_add(2);
+  PLAN_CUDA(cudaMalloc(&d_span, 2 * nrows * sizeof(int64_t)));
+  k_plan_rows<<<(unsigned)((nrows + 255) / 256), 256, 0, st>>>(nrows, npairs, sorted, d_pairptr, rowptr, d_span, d_stat);
+  g_launches.fetch_add(1);
+  std::vector<int64_t> h_span(2 * nrows), h_pairptr(nrows + 1);
   unsigned long long stat[4];
-  int bad = 0;
+  PLAN_CUDA(cudaMemcpyAsync(h_span.data(), d_span, 2 * nrows * sizeof(int64_t), cudaMemcpyDeviceToHost, st));
+  PLAN_CUDA(cudaMemcpyAsync(h_pairptr.data(), d_pairptr, (nrows + 1) * sizeof(int64_t), cudaMemcpyDeviceToHost, st));
   PLAN_CUDA(cudaMemcpyAsync(stat, d_stat, sizeof stat, cudaMemcpyDeviceToHost, st));
-  PLAN_CUDA(cudaMemcpyAsync(&bad, d_bad, sizeof bad, cudaMemcpyDeviceToHost, st));
   PLAN_CUDA(cudaStreamSynchronize(st));
   PLAN_CUDA(cudaGetLastError());
   P->nnz_covered = (int64_t)stat[0]; P->max_row = (int64_t)stat[1]; P->nnz_lo = (int64_t)stat[2]; P->nnz_hi = (int64_t)stat[3];
-  if (!(bad & 3) && P->max_row <= MAXROW) {
-    // Tiles: greedy over the plan rows, on the host (a sequential scan of 8 bytes per row; symbolic phase).  A tile is closed
-    // when its CSR span would exceed the warp's window, at TILE_MAXROWS rows, or at TILE_MAXPAIRS pairs -- so tiles of long
-    // rows (24 pairs on a P2 vertex row) hold 32 rows, one per lane, and tiles of short rows two per lane.
-    std::vector<int64_t> h_span(2 * nrows), h_pairptr(nrows + 1);
-    {
-      int64_t *d_span = nullptr;
-      PLAN_CUDA(cudaMalloc(&d_span, 2 * nrows * sizeof(int64_t)));
-      k_row_spans<<<(unsigned)((nrows + 255) / 256), 256, 0, st>>>(nrows, P->rows, rowptr, d_span);
-      cudaError_t ce = cudaMemcpyAsync(h_span.data(), d_span, 2 * nrows * sizeof(int64_t), cudaMemcpyDeviceToHost, st);
-      if (ce == cudaSuccess) ce = cudaMemcpyAsync(h_pairptr.data(), P->pairptr, (nrows + 1) * sizeof(int64_t), cudaMemcpyDeviceToHost, st);
-      if (ce == cudaSuccess) ce = cudaStreamSynchronize(st);
-      cudaFree(d_span);
-      PLAN_CUDA(ce);
-    }
-    std::vector<int32_t> h_tile_q;
-    std::vector<RowRec> h_rowrec(nrows);
-    h_tile_q.reserve(nrows / 16 + 2);
+  if (P->max_row > MAXROW)
+    PLAN_FAIL(NGSX_ERR_UNSUPPORTED, "rowplan_create: a CSR row is longer than 256 entries; use the coloured scatter (ngsx_assemble_csr_h1)");
+
+  // ---- the schedule, on the host (symbolic phase: a sequential pass over the plan rows) ----
+  // Tiles: greedy over the plan rows; a tile is closed when its CSR span would exceed the warp's window, at TILE_MAXROWS rows
+  // or at TILE_MAXPAIRS pairs.  Lanes: rows by decreasing pair count to the least loaded lane (ties: the lower lane), then
+  // the lanes are renumbered by decreasing load so that the active lanes of every step form a prefix.
+  std::vector<TileHdr> h_tiles;
+  std::vector<int64_t> h_tile_so;                 // first entry of the tile in h_stepoffs
+  std::vector<int32_t> h_stepoffs;                // per tile and step: descriptors before that step
+  std::vector<RowSched> h_sched(nrows);
+  h_tiles.reserve(nrows / 16 + 2);
+  int64_t dcount = 0, max_steps = 0;
+  bool too_many = false;
+  {
+    std::vector<int> order, lane_of(TILE_MAXROWS), start_of(TILE_MAXROWS), rank(32);
     int64_t q0 = 0;
-    h_tile_q.push_back(0);
-    for (int64_t q = 0; q < nrows; q++) {
-      const int64_t np = h_pairptr[q + 1] - h_pairptr[q];
-      if (np > 65535) bad |= 4;
-      if (q > q0 && (h_span[2 * q + 1] - h_span[2 * q0] > ACCW || q - q0 >= TILE_MAXROWS ||
-                     h_pairptr[q + 1] - h_pairptr[q0] > TILE_MAXPAIRS)) {
-        q0 = q;
-        h_tile_q.push_back((int32_t)q);
+    auto close_tile = [&](int64_t qa, int64_t qb) {
+      const int n = (int)(qb - qa);
+      order.resize(n);
+      std::iota(order.begin(), order.end(), 0);
+      std::stable_sort(order.begin(), order.end(), [&](int x, int y) {
+        return h_pairptr[qa + x + 1] - h_pairptr[qa + x] > h_pairptr[qa + y + 1] - h_pairptr[qa + y]; });
+      int load[32] = {0};
+      for (int t = 0; t < n; t++) {
+        const int r = order[t];
+        int best = 0;
+        for (int l = 1; l < 32; l++) if (load[l] < load[best]) best = l;
+        lane_of[r] = best; start_of[r] = load[best];
+        load[best] += (int)(h_pairptr[qa + r + 1] - h_pairptr[qa + r]);
       }
-      RowRec r;
-      r.p0 = (uint32_t)h_pairptr[q]; r.np = (uint16_t)np; r.off = (uint16_t)(h_span[2 * q] - h_span[2 * q0]);
-      h_rowrec[q] = r;
+      int perm[32];
+      std::iota(perm, perm + 32, 0);
+      std::stable_sort(perm, perm + 32, [&](int x, int y) { return load[x] > load[y]; });
+      for (int l = 0; l < 32; l++) rank[perm[l]] = l;
+      TileHdr H{};
+      H.z0 = h_span[2 * qa];
+      H.zlen = (int32_t)(h_span[2 * (qb - 1) + 1] - H.z0);
+      H.d0 = dcount;
+      H.nsteps = load[perm[0]];
+      if (H.nsteps > 255) too_many = true;
+      for (int l = 0; l < 32; l++) H.load[l] = (uint8_t)std::min(255, load[perm[l]]);
+      const int32_t tile = (int32_t)h_tiles.size();
+      h_tile_so.push_back((int64_t)h_stepoffs.size());
+      int32_t acc = 0;
+      for (int s = 0; s < H.nsteps; s++) {
+        h_stepoffs.push_back(acc);
+        int cnt = 0;
+        for (int l = 0; l < 32; l++) cnt += load[l] > s;
+        acc += cnt;
+      }
+      dcount += acc;
+      max_steps = std::max<int64_t>(max_steps, H.nsteps);
+      for (int r = 0; r < n; r++) {
+        RowSched rs;
+        rs.tile = tile; rs.start = start_of[r]; rs.lane = rank[lane_of[r]]; rs.off = (int32_t)(h_span[2 * (qa + r)] - H.z0);
+        h_sched[qa + r] = rs;
+      }
+      h_tiles.push_back(H);
+    };
+    for (int64_t q = 1; q <= nrows; q++) {
+      if (q == nrows || h_span[2 * q + 1] - h_span[2 * q0] > ACCW || q - q0 >= TILE_MAXROWS ||
+          h_pairptr[q + 1] - h_pairptr[q0] > TILE_MAXPAIRS) {
+        close_tile(q0, q);
+        q0 = q;
+      }
     }
-    h_tile_q.push_back((int32_t)nrows);
-    P->ntiles = (int64_t)h_tile_q.size() - 1;
-    PLAN_CUDA(cudaMalloc(&P->tile_q, (P->ntiles + 1) * sizeof(int32_t)));
-    PLAN_CUDA(cudaMalloc(&P->rowrec, nrows * sizeof(RowRec)));
-    PLAN_CUDA(cudaMemcpyAsync(P->tile_q, h_tile_q.data(), (P->ntiles + 1) * sizeof(int32_t), cudaMemcpyHostToDevice, st));
-    PLAN_CUDA(cudaMemcpyAsync(P->rowrec, h_rowrec.data(), nrows * sizeof(RowRec), cudaMemcpyHostToDevice, st));
-    PLAN_CUDA(cudaStreamSynchronize(st));          // the host vectors go out of use only after the copies
-    g_launches.fetch_add(1);
-    // tile processing order
-    uint32_t *ck = nullptr, *ck2 = nullptr;
-    int32_t *ci2 = nullptr, *order = nullptr;
-    PLAN_CUDA(cudaMalloc(&ck, P->ntiles * sizeof(uint32_t)));
-    PLAN_CUDA(cudaMalloc(&ck2, P->ntiles * sizeof(uint32_t)));
-    PLAN_CUDA(cudaMalloc(&ci2, P->ntiles * sizeof(int32_t)));
-    PLAN_CUDA(cudaMalloc(&order, P->ntiles * sizeof(int32_t)));
-    PLAN_CUDA(cudaMemsetAsync(d_stat, 0, sizeof(unsigned long long), st));
-    k_tile_keys<<<(unsigned)((P->ntiles + 255) / 256), 256, 0, st>>>(P->ntiles, P->tile_q, P->pairptr, P->desc, P->ds, ck, ci2, d_stat);
-    cudaFree(tmp); tmp = nullptr; tmp_bytes = 0;
-    PLAN_CUDA(cub::DeviceRadixSort::SortPairs(nullptr, tmp_bytes, ck, ck2, ci2, order, (int)P->ntiles, 0, 32, st));
-    PLAN_CUDA(cudaMalloc(&tmp, tmp_bytes));
-    PLAN_CUDA(cub::DeviceRadixSort::SortPairs(tmp, tmp_bytes, ck, ck2, ci2, order, (int)P->ntiles, 0, 32, st));
-    g_launches.fetch_add(5);
-    unsigned long long nonempty = 0;
-    PLAN_CUDA(cudaMemcpyAsync(&nonempty, d_stat, sizeof nonempty, cudaMemcpyDeviceToHost, st));
-    PLAN_CUDA(cudaMemcpyAsync(&bad, d_bad, sizeof bad, cudaMemcpyDeviceToHost, st));
-    PLAN_CUDA(cudaStreamSynchronize(st));
-    P->ntiles_active = (int64_t)nonempty;
-    PLAN_CUDA(cudaMalloc(&P->tile_info, std::max<int64_t>(1, P->ntiles_active) * sizeof(TileInfo)));
-    PLAN_CUDA(cudaMalloc(&P->tile_split, std::max<int64_t>(1, P->ntiles_active) * 33 * sizeof(int32_t)));
-    if (P->ntiles_active > 0)
-      k_tile_tables<<<(unsigned)((P->ntiles_active * 33 + 255) / 256), 256, 0, st>>>(P->ntiles_active, order, P->tile_q, P->rows, rowptr, P->pairptr,
-                                                                                   P->tile_info, P->tile_split);
-    g_launches.fetch_add(1);
-    PLAN_CUDA(cudaStreamSynchronize(st));
-    cudaFree(ck); cudaFree(ck2); cudaFree(ci2); cudaFree(order);
-    PLAN_CUDA(cudaGetLastError());
   }
+  if (too_many) PLAN_FAIL(NGSX_ERR_UNSUPPORTED, "rowplan_create: a dof with more than 255 adjacent list entries; use the coloured scatter");
+  if (dcount != npairs) PLAN_FAIL(NGSX_ERR_CUDA, "rowplan_create: internal error (schedule does not cover the pairs)");
+  P->ntiles = (int64_t)h_tiles.size();
+  P->max_steps = max_steps;
+  std::vector<int64_t> h_tile_d0(P->ntiles);
+  for (int64_t c = 0; c < P->ntiles; c++) h_tile_d0[c] = h_tiles[c].d0;
+
+  PLAN_CUDA(cudaMalloc(&d_tiles_nat, P->ntiles * sizeof(TileHdr)));
+  PLAN_CUDA(cudaMalloc(&P->tiles, P->ntiles * sizeof(TileHdr)));
+  PLAN_CUDA(cudaMalloc(&d_tile_d0, P->ntiles * sizeof(int64_t)));
+  PLAN_CUDA(cudaMalloc(&d_tile_so, P->ntiles * sizeof(int64_t)));
+  PLAN_CUDA(cudaMalloc(&d_stepoffs, std::max<size_t>(1, h_stepoffs.size()) * sizeof(int32_t)));
+  PLAN_CUDA(cudaMalloc(&d_sched, nrows * sizeof(RowSched)));
+  PLAN_CUDA(cudaMalloc(&P->desc, (size_t)npairs * P->ds));
+  PLAN_CUDA(cudaMemcpyAsync(d_tiles_nat, h_tiles.data(), P->ntiles * sizeof(TileHdr), cudaMemcpyHostToDevice, st));
+  PLAN_CUDA(cudaMemcpyAsync(d_tile_d0, h_tile_d0.data(), P->ntiles * sizeof(int64_t), cudaMemcpyHostToDevice, st));
+  PLAN_CUDA(cudaMemcpyAsync(d_tile_so, h_tile_so.data(), P->ntiles * sizeof(int64_t), cudaMemcpyHostToDevice, st));
+  PLAN_CUDA(cudaMemcpyAsync(d_stepoffs, h_stepoffs.data(), h_stepoffs.size() * sizeof(int32_t), cudaMemcpyHostToDevice, st));
+  PLAN_CUDA(cudaMemcpyAsync(d_sched, h_sched.data(), nrows * sizeof(RowSched), cudaMemcpyHostToDevice, st));
+  PLAN_CUDA(cudaMemsetAsync(P->desc, 0, (size_t)npairs * P->ds, st));
+  k_plan_desc<<<(unsigned)((npairs + 127) / 128), 128, 0, st>>>(npairs, nrows, nd, nlist, P->ds, sorted, d_pairptr, d_sched, d_tile_d0, d_tile_so,
+                                                               d_stepoffs, table, rowptr, colidx, P->desc, d_bad);
+  // tile processing order
+  PLAN_CUDA(cudaMalloc(&d_ck, P->ntiles * sizeof(uint32_t)));
+  PLAN_CUDA(cudaMalloc(&d_ck2, P->ntiles * sizeof(uint32_t)));
+  PLAN_CUDA(cudaMalloc(&d_ids, P->ntiles * sizeof(int32_t)));
+  PLAN_CUDA(cudaMalloc(&d_order, P->ntiles * sizeof(int32_t)));
+  k_tile_keys<<<(unsigned)((P->ntiles + 255) / 256), 256, 0, st>>>(P->ntiles, d_tiles_nat, P->desc, P->ds, d_ck, d_ids);
+  cudaFree(tmp); tmp = nullptr; tmp_bytes = 0;
+  PLAN_CUDA(cub::DeviceRadixSort::SortPairs(nullptr, tmp_bytes, d_ck, d_ck2, d_ids, d_order, (int)P->ntiles, 0, 32, st));
+  PLAN_CUDA(cudaMalloc(&tmp, tmp_bytes));
+  PLAN_CUDA(cub::DeviceRadixSort::SortPairs(tmp, tmp_bytes, d_ck, d_ck2, d_ids, d_order, (int)P->ntiles, 0, 32, st));
+  k_tile_permute<<<(unsigned)((P->ntiles + 255) / 256), 256, 0, st>>>(P->ntiles, d_order, d_tiles_nat, P->tiles);
+  g_launches.fetch_add(5);
+  int bad = 0;
+  PLAN_CUDA(cudaMemcpyAsync(&bad, d_bad, sizeof bad, cudaMemcpyDeviceToHost, st));
+  PLAN_CUDA(cudaStreamSynchronize(st));          // the host vectors go out of use only after the copies
+  PLAN_CUDA(cudaGetLastError());
+  if (bad & 1)
+    PLAN_FAIL(NGSX_ERR_ARG, "rowplan_create: an element coupling is missing from the sparsity pattern (element_restriction too small?)");
+  if (bad & 2)
+    PLAN_FAIL(NGSX_ERR_UNSUPPORTED, "rowplan_create: a CSR row is longer than 256 entries; use the coloured scatter (ngsx_assemble_csr_h1)");
 #undef PLAN_CUDA
+#undef PLAN_FAIL
   cleanup();
-  if (bad & 1) {
-    set_error("rowplan_create: an element coupling is missing from the sparsity pattern (element_restriction too small?)");
-    ngsx_rowplan_destroy(P); *out = nullptr;
-    return NGSX_ERR_ARG;
-  }
-  if (bad & 4) {
-    set_error("rowplan_create: a dof with more than 65535 adjacent elements");
-    ngsx_rowplan_destroy(P); *out = nullptr;
-    return NGSX_ERR_UNSUPPORTED;
-  }
-  if ((bad & 2) || P->max_row > MAXROW) {
-    set_error("rowplan_create: a CSR row is longer than 256 entries; use the coloured scatter (ngsx_assemble_csr_h1)");
-    ngsx_rowplan_destroy(P); *out = nullptr;
-    return NGSX_ERR_UNSUPPORTED;
-  }
   return NGSX_OK;
 }
 

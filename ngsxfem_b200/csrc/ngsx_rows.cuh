@@ -1,42 +1,58 @@
-// ngsx_rows.cuh -- the owner-computes ("row gather") assembly plan shared by ngsx_rows.cu (plan construction, row kernel)
-// and ngsx_assemble.cu (geometry-factor / cut-element passes that feed it).
+// ngsx_rows.cuh -- the owner-computes ("row gather") assembly plan shared by ngsx_rows.cu (plan construction, row kernel),
+// ngsx_rowsmat.cu (gather of precomputed blocks) and ngsx_assemble.cu (geometry / cut-element passes that feed them).
+//
+// Plan = a static schedule.  The non-empty CSR rows of the plan are cut into TILES of consecutive rows whose values fit a warp's
+// shared-memory window; inside a tile every row belongs to one LANE (longest-processing-time assignment: rows by decreasing pair
+// count to the least loaded lane, lanes then numbered by decreasing load), and the lane walks the (row, element) pairs of its
+// rows one per STEP.  The 16-byte pair descriptors are stored step-major, lane-minor and without padding: the lanes active in
+// step s are the prefix [0, cnt(s)), so the warp reads one contiguous run of descriptors per step (coalesced 128-bit loads).
+// A descriptor carries everything the lane needs -- no per-row records, no split tables:
+//   word 0      k | i << 27      list index of the element (27 bits) and local row i (5 bits)
+//   word 1      off | pos[0] << 16 | pos[1] << 24      offset of the row inside the tile's window; positions of the local columns
+//   words 2, 3  pos[2..9]        (32-byte descriptors, 10 < nd <= 26: four more words with pos[10..25])
+// The same numbering addresses PACKED block rows (ngsx_rowplan_rowslots): slot = index of the pair's descriptor.
 #pragma once
 #include "ngsx_host.cuh"
 
-// One (row, element) pair descriptor, 16 bytes (one LDG.128):
-//   int32 k        list index of the element
-//   uint8 i        local row (the dof of the row inside element k)
-//   uint8 pos[nd]  position of local column j inside the CSR row (nd <= 11; 32-byte descriptors for 11 < nd <= 27:
-//                  the merged dof lists of facet patches)
 namespace ngsx {
-struct RowRec { uint32_t p0; uint16_t np; uint16_t off; };   // first pair, number of pairs, offset of the row inside its tile
-struct TileInfo { int64_t z0; int32_t zlen; int32_t pad; };  // CSR span of a tile
-}
+struct TileHdr {             // 64 bytes
+  int64_t z0;                // first CSR entry of the tile's span
+  int64_t d0;                // first descriptor (= slot) of the tile
+  int32_t zlen, nsteps;      // CSR entries in the span; steps = pairs of the most loaded lane
+  uint8_t load[32];          // pairs per lane, non-increasing
+  int32_t pad[2];
+};
+static_assert(sizeof(TileHdr) == 64, "tile header layout");
+constexpr uint32_t DESC_KBITS = 27;
+constexpr uint32_t DESC_KMASK = (1u << DESC_KBITS) - 1u;
+
+// moments of a permutation-symmetric reference rule over the barycentrics (host-computed, kernel argument):
+// m0 = sum w, m1 = sum w l_a, m2s = sum w l_a^2, m2d = sum w l_a l_b, m3aab, m3abc, m4aabb, m4aabc, m4abcd
+struct RuleMom { double m0, m1, m2s, m2d, m3aab, m3abc, m4aabb, m4aabc, m4abcd; };
+}  // namespace ngsx
+
 struct ngsx_rowplan {
   int64_t nlist = 0, ndof = 0, npairs = 0, nrows = 0, nnz_covered = 0, max_row = 0, nnz_lo = 0, nnz_hi = 0;
   int32_t nd = 0, ds = 0;
-  int32_t *rows = nullptr;          // [nrows] dof number of the non-empty rows, ascending
-  int64_t *pairptr = nullptr;       // [nrows + 1]
-  uint8_t *desc = nullptr;          // [npairs][ds]
-  ngsx::RowRec *rowrec = nullptr;   // [nrows]
-  int32_t *tile_q = nullptr;        // [ntiles + 1] first plan row of each tile (natural order)
-  ngsx::TileInfo *tile_info = nullptr;  // [ntiles_active] in processing order
-  int32_t *tile_split = nullptr;    // [ntiles_active][33] first plan row of each lane's row range (pair-balanced)
-  int64_t ntiles = 0, ntiles_active = 0;
+  int64_t ntiles = 0;               // non-empty tiles
+  int64_t nslots = 0;               // == npairs (no padding)
+  int64_t max_steps = 0;
+  ngsx::TileHdr *tiles = nullptr;   // [ntiles] in processing order
+  uint8_t *desc = nullptr;          // [nslots][ds]
+  int32_t *rowslot = nullptr;       // [nlist][nd] slot of pair (k, i) or -1; built on first request
   const int64_t *rowptr = nullptr;  // caller-owned CSR (must outlive the plan)
-  // scratch of the numeric phase, allocated on first use
-  double *G = nullptr;              // [nlist][8] geometry factors + code
+  // scratch of the numeric phase of ngsx_assemble_csr_rows_h1, allocated on first use
+  double *G = nullptr;              // [nlist][dim+1][4] per local vertex a: K[a][0..dim-1], (pad), |det J| c_mass  -- or a NaN-boxed code
   int32_t *cutlist = nullptr;       // [nlist] list indices of the elements that need quadrature
-  int32_t *cutcount = nullptr;      // [1]
-  double *cutmats = nullptr;        // [nlist][nd*nd]
-  double *tab = nullptr;            // [(npair+1)][nd*nd] reference tables of the constant-rule path
-  const void *tab_rule = nullptr;   // rule the tables were computed for (they depend on the reference rule only: computed once)
-  int tab_key = 0;
+  int32_t *cutcount = nullptr;      // [1] work-list length of the last call (may exceed cut_cap: the overflow is reported)
+  double *cutmats = nullptr;        // [cut_cap][nd*nd]
+  int64_t cut_cap = 0;
+  int g_dim = 0;
 };
 
 namespace ngsx {
 
-// tuning knobs (overridable with -D for sweeps; the defaults are the measured best on B200 at config 2)
+// tuning knobs (overridable with -D for sweeps)
 #ifndef NGSX_RW
 #define NGSX_RW 4
 #endif
@@ -52,32 +68,20 @@ namespace ngsx {
 #ifndef NGSX_TILE_MAXPAIRS
 #define NGSX_TILE_MAXPAIRS 768
 #endif
-constexpr int RW = NGSX_RW;                        // warps per CTA of the row kernel
+constexpr int RW = NGSX_RW;                        // warps per CTA of the row kernels
 constexpr int MAXROW = 256;                        // longest supported CSR row (column positions are bytes)
-constexpr int ACCW = NGSX_ACCW;                    // doubles of shared memory per warp: the CSR span of one tile (11 KB -> 4 CTAs = 16 warps per SM)
-constexpr int TILE_MAXROWS = NGSX_TILE_MAXROWS;    // rows per tile (2 per lane) ...
-constexpr int TILE_MAXPAIRS = NGSX_TILE_MAXPAIRS;  // ... and (row, element) pairs per tile (24 per lane)
+constexpr int ACCW = NGSX_ACCW;                    // doubles of shared memory per warp: the CSR span of one tile
+constexpr int TILE_MAXROWS = NGSX_TILE_MAXROWS;
+constexpr int TILE_MAXPAIRS = NGSX_TILE_MAXPAIRS;
 
-__device__ __forceinline__ RowRec ld_rowrec(const RowRec *p) {
-  const uint2 u = __ldg(reinterpret_cast<const uint2 *>(p));
-  RowRec r;
-  r.p0 = u.x; r.np = (uint16_t)(u.y & 0xffffu); r.off = (uint16_t)(u.y >> 16);
-  return r;
-}
+// NaN-boxed code in the mass slot of a geometry record: quiet NaN | payload; payload 0 = the element contributes nothing,
+// s + 1 = row s of cutmats
+constexpr unsigned long long GCODE_NAN = 0x7ff8000000000000ULL;
 
-// reference tables of the constant-rule path (k_ref_tables -> k_rows):  [0, nd^2) mass table Tm[i][j];  then per shape i the
-// gradient-moment block cM[i][a][n] (dim x (dim+1) doubles) at stride CS -- CS/2 is odd so that the 16-byte shared-memory
-// slots of different i fall into different bank groups
-template <int DIM> struct RefTab {
-  static constexpr int CS = DIM == 3 ? 14 : 6;
-  static __host__ __device__ constexpr int cm_offset(int ne) { return (ne + 1) & ~1; }    // 16-byte aligned start of the cM blocks
-};
-
-// geometry-factor record (8 doubles per list entry): g[0..5] = |det J| c_stiff (J^-1 J^-T) upper triangle, g[6] = |det J| c_mass,
-// g[7] = code as int64: -1 no contribution, 0 constant-rule element, s+1 = row s of cutmats
-constexpr int GSTRIDE = 8;
-
-int rows_scratch(ngsx_rowplan *plan, int npairtab);
-int launch_rows(const ngsx_rowplan *plan, int npairtab, int accumulate, double *vals, int sm_count, cudaStream_t st);
+int rows_scratch(ngsx_rowplan *plan, int dim);
+int rows_reserve_cut(ngsx_rowplan *plan, int64_t cap);
+// moments of the reference rule of a dim-simplex; false if the rule is not permutation symmetric (or not tabulated)
+bool rule_moments(int dim, int order, RuleMom *out);
+int launch_rows(const ngsx_rowplan *plan, int dim, const RuleMom &mom, int accumulate, double *vals, int sm_count, cudaStream_t st);
 
 }  // namespace ngsx

@@ -388,6 +388,7 @@ extern "C" int ngsx_xfem_elmat_h1(const ngsx_mesh *mesh, const double *lset_v, i
     }
     X.cls[9] = (int8_t)o;
   }
+  if (take_packed_output()) { set_error("packed output is not served by this entry point yet"); return NGSX_ERR_UNSUPPORTED; }
   if (nlist == 0) return NGSX_OK;
   cudaStream_t st = as_stream(stream);
   switch (mesh->dim * 10 + fe_order) {
