@@ -464,6 +464,16 @@ class _RowPlan:
             pass
 
 
+def _packed_rows(plan, nd):
+    """row-slot map of a plan (device pointer) and the packed rows buffer [nslots][nd rounded up to even], allocated once"""
+    if getattr(plan, "rows", None) is None:
+        p, ns = ctypes.c_void_p(), ctypes.c_int64(0)
+        check(_lib_().ngsx_rowplan_rowslots(plan.handle, ctypes.byref(p), ctypes.byref(ns), _stream()))
+        plan.slots = p
+        plan.rows = torch.zeros(max(1, ns.value) * (nd + (nd & 1)), dtype=torch.float64, device=plan.els.device)
+    return plan.slots, plan.rows
+
+
 def color_list(table: torch.Tensor, ndof: int, group: int):
     """ngsx_color_groups on the host copy of a dof table [n][nd]; returns (perm (device), color_ptr list)"""
     n, nd = table.shape
@@ -722,19 +732,23 @@ class BilinearForm:
                 # written once, plan order, no atomics)
                 lv = _lset_vec(integ.lset)
                 n = plan.els.numel()
-                if getattr(plan, "mats", None) is None:
-                    plan.mats = torch.empty((n, fes.nd * fes.nd), dtype=torch.float64, device=fes.mesh.device)
                 if self._deformation_of(integ) is not None:
                     if fes.order >= 3:
                         raise NgsxError(-2, "H1 order 3 on a deformed mesh is outside the CUDA path; no CPU fallback")
+                    # packed block rows: the kernel writes row i of block k where the gather's schedule reads it (ngsx_rowplan_rowslots)
+                    slots, rows = _packed_rows(plan, fes.nd)
                     defo = fes.mesh.c_deformation(self._deformation_of(integ))
+                    L.ngsx_set_packed_output(slots)
                     check(L.ngsx_elmat_h1_deformed(mesh_c, ctypes.byref(defo), _ptr(lv), fes.order, integ.dt, integ.intorder(fes.order),
-                                                   ctypes.byref(integ.form), n, _ptr(plan.els), _ptr(plan.mats), None, _ptr(self._err[k]), _stream()))
+                                                   ctypes.byref(integ.form), n, _ptr(plan.els), _ptr(rows), None, _ptr(self._err[k]), _stream()))
                     self._err_armed = True
+                    check(L.ngsx_assemble_csr_rows_packed(plan.handle, _ptr(rows), 0 if overwrite else 1, _ptr(self.mat.vals), _stream()))
                 else:
+                    if getattr(plan, "mats", None) is None:
+                        plan.mats = torch.empty((n, fes.nd * fes.nd), dtype=torch.float64, device=fes.mesh.device)
                     check(L.ngsx_elmat_h1(mesh_c, _ptr(lv), fes.order, integ.dt, integ.intorder(fes.order), ctypes.byref(integ.form), n,
                                           _ptr(plan.els), _ptr(plan.mats), None, _stream()))
-                check(L.ngsx_assemble_csr_rows_mats(plan.handle, _ptr(plan.mats), 0 if overwrite else 1, _ptr(self.mat.vals), _stream()))
+                    check(L.ngsx_assemble_csr_rows_mats(plan.handle, _ptr(plan.mats), 0 if overwrite else 1, _ptr(self.mat.vals), _stream()))
             elif isinstance(plan, _RowPlan):
                 lv = _lset_vec(integ.lset)
                 if gather_after is not None:
@@ -766,12 +780,26 @@ class BilinearForm:
                 return
             self._err_armed = False
             err = self._err.tolist()
+            self._check_cut_capacity()
         else:
             err = err.tolist()
         n, first = sum(r[0] for r in err), min(r[1] for r in err)
         if n:
             raise NgsxError(-4, f"{n} element(s) carry a level set the reference rejects (first: element {first}): "
                                 "'You tried to cut a simplex with a plain geometry lset function'")
+
+    def _check_cut_capacity(self):
+        """the cut-element buffer of a row plan is sized on its first numeric call; a level set that needs more is reported here
+        (the excess elements of that Assemble were skipped): the buffer is grown and the caller assembles again"""
+        L = _lib_()
+        for plan in self._plans.values():
+            for pl in (plan, getattr(plan, "plan_a", None)):
+                if isinstance(pl, _RowPlan) and pl.handle is not None:
+                    cnt, cap = ctypes.c_int64(0), ctypes.c_int64(0)
+                    check(L.ngsx_rowplan_cut_usage(pl.handle, ctypes.byref(cnt), ctypes.byref(cap), _stream()))
+                    if cap.value and cnt.value > cap.value:
+                        check(L.ngsx_rowplan_reserve_cut(pl.handle, 2 * cnt.value))
+                        raise NgsxError(-5, f"{cnt.value} cut elements exceeded the plan's buffer ({cap.value}); it has been grown: Assemble again")
 
     def degenerate_flags(self):
         """device tensor [{count, first element}] per integrator of the last Assemble, for callers that download it on their

@@ -1354,3 +1354,69 @@ def test_order3_single_elements_vertex_permutations(X, golden_single, dim):
         f.Assemble()
         want = orc.assemble_vec(dim, el2v, vert, lsv, 3, Vh.el2dof.cpu().numpy(), Vh.ndof, dt, 6, [(1.0, 0, 0, 0), (1.0, 1, 1, 0)])
         assert np.abs(f.vec.cpu().numpy() - want).max() <= RTOL * np.abs(want).max()
+
+
+@pytest.mark.parametrize("dim,fo", [(2, 1), (2, 2), (3, 1), (3, 2)])
+def test_packed_rows_equal_dense_blocks(X, dim, fo):
+    """the two sources of the matrix gather (dense blocks fetched per lane / packed rows written by the producer at the slots of
+    the schedule) give bitwise the same CSR values: same plan, same summation order"""
+    m = X.meshes.MakeStructured2DMesh(14) if dim == 2 else X.meshes.MakeStructured3DMesh(6)
+    mesh = X.ngs.Mesh(m)
+    gf = X.ngs.GridFunction(X.ngs.H1(mesh, order=1))
+    X.xfem.InterpolateToP1(X.ngs.SphereLevelset((0.5,) * dim, 0.33), gf)
+    Vd = X.ngs.H1(mesh, order=2, dim=dim)
+    defo = X.ngs.GridFunction(Vd)
+    rng = np.random.default_rng(3)
+    defo.vec.copy_(dev(0.01 * rng.uniform(-1, 1, (Vd.ndof, dim))))
+    mesh.SetDeformation(defo)
+    Vh = X.ngs.H1(mesh, order=fo)
+    u, v = Vh.TnT()
+    L = X.lib.load()
+    st = torch.cuda.current_stream().cuda_stream
+    for dt in (NEG, IF):
+        a = X.xfem.BilinearForm(Vh)
+        a += X.xfem.SymbolicBFI(levelset_domain={"levelset": gf, "domain_type": dt}, form=0.7 * X.ngs.grad(u) * X.ngs.grad(v) + 1.3 * u * v)
+        a.Assemble()                                                             # packed rows
+        plan, integ = a._plans[0], a.integrators[0]
+        assert getattr(plan, "rows", None) is not None
+        n = plan.els.numel()
+        mats = torch.empty((n, Vh.nd * Vh.nd), dtype=torch.float64, device="cuda")
+        d = mesh.c_deformation()
+        X.lib.check(L.ngsx_elmat_h1_deformed(ctypes.byref(mesh.c_struct()), ctypes.byref(d), gf.vec.data_ptr(), fo, dt, integ.intorder(fo),
+                                             ctypes.byref(integ.form), n, plan.els.data_ptr(), mats.data_ptr(), None, None, st))
+        vals = torch.full_like(a.mat.vals, float("nan"))
+        X.lib.check(L.ngsx_assemble_csr_rows_mats(plan.handle, mats.data_ptr(), 0, vals.data_ptr(), st))
+        assert torch.equal(vals, a.mat.vals)
+        # accumulate: twice the operator
+        X.lib.check(L.ngsx_assemble_csr_rows_mats(plan.handle, mats.data_ptr(), 1, vals.data_ptr(), st))
+        assert torch.equal(vals, 2 * a.mat.vals)
+    mesh.UnsetDeformation()
+
+
+def test_cut_buffer_grows_with_the_level_set(X):
+    """the plan's cut-element buffer is sized on the first Assemble; a level set that cuts many more elements is reported by
+    check_degenerate (NGSX_ERR_CAPACITY), the buffer grows, and the second Assemble equals a fresh form's"""
+    mesh = X.ngs.Mesh(X.meshes.MakeStructured3DMesh(16))
+    gf = X.ngs.GridFunction(X.ngs.H1(mesh, order=1))
+    X.xfem.InterpolateToP1(X.ngs.SphereLevelset((0.5, 0.5, 0.5), 0.05), gf)
+    Vh = X.ngs.H1(mesh, order=2)
+    u, v = Vh.TnT()
+    form = X.ngs.grad(u) * X.ngs.grad(v) + u * v
+    a = X.xfem.BilinearForm(Vh)
+    a += X.xfem.SymbolicBFI(levelset_domain={"levelset": gf, "domain_type": NEG}, form=form)
+    a.Assemble()
+    a.check_degenerate()
+    n_small = int((X.xfem.CutInfo(mesh, gf).dom == IF).sum())
+    X.xfem.InterpolateToP1(X.ngs.SphereLevelset((0.5, 0.5, 0.5), 0.45), gf)
+    n_big = int((X.xfem.CutInfo(mesh, gf).dom == IF).sum())
+    assert n_big > 1.25 * n_small + 1024
+    a.Assemble()
+    with pytest.raises(X.lib.NgsxError) as exc:
+        a.check_degenerate()
+    assert exc.value.status == -5
+    a.Assemble()
+    a.check_degenerate()
+    b = X.xfem.BilinearForm(Vh)
+    b += X.xfem.SymbolicBFI(levelset_domain={"levelset": gf, "domain_type": NEG}, form=form)
+    b.Assemble()
+    assert torch.equal(a.mat.vals, b.mat.vals)
