@@ -288,6 +288,23 @@ int ngsx_st_rule_fill(const ngsx_mesh *mesh, const double *lset_st, int ntime_do
 int ngsx_st_integrate(const ngsx_mesh *mesh, const double *lset_st, int ntime_dofs, int dt, int order_space, int order_time,
                       const ngsx_poly *h_f, const int32_t *h_texp, double *out, void *stream);
 
+/* ---- (f-5) quadrilaterals / hexahedra ------------------------------------------------------------------------------
+ * LevelsetCutQuadrilateral (cutint/straightcutrule.cpp:206-501, policy FIND_OPTIMAL) and the ET_QUAD / ET_HEX branch of
+ * StraightCutIntegrationRule[Untransformed] (:580-726).  For these entry points mesh->el2v is [ne][4] (dim 2) / [ne][8] (dim 3)
+ * in NGSolve's local vertex order ((0,0), (1,0), (1,1), (0,1) [, the same at the upper face]); the level set is the multilinear
+ * interpolant of the vertex values lset_v, the geometry the multilinear map of the vertices.  err as in ngsx_classify: elements
+ * on which the reference throws (a slice that is not cut, an exact zero) -- and hexahedra that would take the reference's
+ * fallback to tetrahedra (unreachable with a finite gradient) -- are counted, get no points and dom = -1.
+ * ngsx_q_classify: CutInformation::Update (xfem/cutinfo.cpp:54-120): dom [ne] int8, cut ratio [ne] (order-0 part volumes).
+ * ngsx_q_rule_count / _fill: as ngsx_rule_count / ngsx_rule_fill (reference coordinates, the reference's emission order; uncut
+ * elements of the domain carry the tensor Gauss rule).  ngsx_q_integrate: IntegrateX (cutint/python_cutint.cpp:20-72). */
+int ngsx_q_classify(const ngsx_mesh *mesh, const double *lset_v, int8_t *dom, double *ratio, int64_t *err, void *stream);
+int ngsx_q_rule_count(const ngsx_mesh *mesh, const double *lset_v, int dt, int order, int32_t *npts, int64_t *err, void *stream);
+int ngsx_q_rule_fill(const ngsx_mesh *mesh, const double *lset_v, int dt, int order, int transform_if, const int64_t *offs,
+                     double *pts3, double *wts, void *stream);
+int ngsx_q_integrate(const ngsx_mesh *mesh, const double *lset_v, int dt, int order, const ngsx_poly *h_f, double *out, int64_t *err,
+                     void *stream);
+
 /* ---- facet / element / dof marking ----------------------------------------------------------------------------- */
 /* facet2el [nf][2], -1 = no neighbour (boundary facet: bnd_val_a/b are used, xfem/cutinfo.cpp:238-241) */
 int ngsx_facets_neighbor_types(int64_t nf, const int32_t *facet2el, const uint32_t *a_words, const uint32_t *b_words,

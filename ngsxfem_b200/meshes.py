@@ -134,7 +134,33 @@ class SimplexMesh:
         return self._cache[key]
 
 
-def MakeStructured2DMesh(nx=10, ny=None, device="cpu", lo=(0.0, 0.0), hi=(1.0, 1.0)) -> SimplexMesh:
+@dataclass
+class TensorMesh:
+    """Flat-array mesh of quadrilaterals / hexahedra: ``el2v[ne][2^dim]`` in NGSolve's local vertex order ((0,0), (1,0), (1,1),
+    (0,1) [, the same at the upper face]); SURVEY section 8 row f-5.  Only what the cut-quadrature path needs (P1 level sets)."""
+    dim: int
+    vert: torch.Tensor
+    el2v: torch.Tensor
+    tensor = True
+
+    @property
+    def ne(self):
+        return self.el2v.shape[0]
+
+    @property
+    def nv(self):
+        return self.vert.shape[0]
+
+    @property
+    def device(self):
+        return self.vert.device
+
+    def h1_dofs(self, order):
+        assert order == 1, "tensor-product cells carry the (multilinear) level set only"
+        return self.el2v, self.nv
+
+
+def MakeStructured2DMesh(nx=10, ny=None, device="cpu", lo=(0.0, 0.0), hi=(1.0, 1.0), quads=False):
     """Triangles of NGS/python/meshes.py:75-121 (quads=False): vertex id = i*(nx+1)+j at (j/nx, i/ny);
     per cell trigs [base, base+1, base+nx+1] and [base+1, base+nx+2, base+nx+1].  ``lo/hi`` apply the affine
     ``mapping`` the reference allows (e.g. the [-1,1]^2 square of fictdom_ghostpen.py)."""
@@ -149,13 +175,16 @@ def MakeStructured2DMesh(nx=10, ny=None, device="cpu", lo=(0.0, 0.0), hi=(1.0, 1
         vert = lo_t + vert * (hi_t - lo_t)
     ci, cj = torch.meshgrid(torch.arange(ny, device=device), torch.arange(nx, device=device), indexing="ij")
     base = (ci * (nx + 1) + cj).reshape(-1)
+    if quads:                                       # NGS/python/meshes.py:113-119: pnum = [base, base+1, base+nx+2, base+nx+1]
+        el2v = torch.stack([base, base + 1, base + nx + 2, base + nx + 1], dim=1).to(torch.int32).contiguous()
+        return TensorMesh(2, vert.contiguous(), el2v)
     t1 = torch.stack([base, base + 1, base + nx + 1], dim=1)
     t2 = torch.stack([base + 1, base + nx + 2, base + nx + 1], dim=1)
     el2v = torch.stack([t1, t2], dim=1).reshape(-1, 3).to(torch.int32).contiguous()
     return SimplexMesh(2, vert.contiguous(), el2v)
 
 
-def MakeStructured3DMesh(nx=10, ny=None, nz=None, device="cpu", lo=(0.0, 0.0, 0.0), hi=(1.0, 1.0, 1.0)) -> SimplexMesh:
+def MakeStructured3DMesh(nx=10, ny=None, nz=None, device="cpu", lo=(0.0, 0.0, 0.0), hi=(1.0, 1.0, 1.0), hexes=False):
     """Kuhn tets of NGS/python/meshes.py:259-313 (hexes=False): vertex id = i*(ny+1)*(nz+1)+j*(nz+1)+k at
     (i/nx, j/ny, k/nz); 6 tets per cube in the reference's order; element order is cube-major."""
     ny = nx if ny is None else ny
@@ -175,6 +204,8 @@ def MakeStructured3DMesh(nx=10, ny=None, nz=None, device="cpu", lo=(0.0, 0.0, 0.
     up = base + (ny + 1) * (nz + 1)
     pnum = torch.stack([base, base + 1, base + (nz + 1) + 1, base + (nz + 1),
                         up, up + 1, up + (nz + 1) + 1, up + (nz + 1)], dim=1)
+    if hexes:                                       # NGS/python/meshes.py:296-304: the cube's eight corners in pnum order
+        return TensorMesh(3, vert.contiguous(), pnum.to(torch.int32).contiguous())
     q = torch.tensor(KUHN_TETS, device=device, dtype=torch.long)          # 6 x 4
     el2v = pnum[:, q].reshape(-1, 4).to(torch.int32).contiguous()
     return SimplexMesh(3, vert.contiguous(), el2v)

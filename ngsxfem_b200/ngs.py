@@ -10,7 +10,7 @@ from typing import Dict, List, Optional, Tuple
 import torch
 
 from . import _lib
-from .meshes import SimplexMesh
+from .meshes import SimplexMesh, TensorMesh
 
 VOL, BND = 0, 1
 
@@ -96,8 +96,34 @@ class BitArray:
 
 
 # ------------------------------------------------------------------------------------------------------------------
+class QMesh(TensorMesh):
+    """device-resident mesh of quadrilaterals / hexahedra (row f-5): cut quadrature only (CutInfo, Integrate, rule API)"""
+
+    def __init__(self, m: TensorMesh, device="cuda"):
+        super().__init__(m.dim, m.vert.to(device).contiguous(), m.el2v.to(device).contiguous())
+        self._c = None
+        self.deformation = None
+
+    def c_struct(self) -> _lib.Mesh:
+        if self._c is None:
+            require_cuda(self.vert, "mesh")
+            self._c = _lib.Mesh(self.dim, 0, self.ne, self.nv, self.vert.data_ptr(), self.el2v.data_ptr())
+        return self._c
+
+    def c_deformation(self, gf=None):
+        return None
+
+    def GetNE(self, vb=VOL):
+        return self.ne
+
+
 class Mesh(SimplexMesh):
-    """device-resident simplex mesh + the ngsx_mesh struct of the C ABI"""
+    """device-resident simplex mesh + the ngsx_mesh struct of the C ABI (a TensorMesh gives a QMesh)"""
+
+    def __new__(cls, m=None, device="cuda"):
+        if isinstance(m, TensorMesh):
+            return QMesh(m, device)
+        return super().__new__(cls)
 
     def __init__(self, m: SimplexMesh, device="cuda"):
         super().__init__(m.dim, m.vert.to(device).contiguous(), m.el2v.to(device).contiguous())

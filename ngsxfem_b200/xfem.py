@@ -82,6 +82,13 @@ class CutInfo:
             raise NgsxError(-2, "space-time CutInfo (time_order >= 0) is outside the CUDA path")
         lv = _lset_vec(levelset)
         L = _lib_()
+        if getattr(self.mesh, "tensor", False):                      # quadrilaterals / hexahedra (row f-5)
+            check(L.ngsx_q_classify(ctypes.byref(self.mesh.c_struct()), _ptr(lv), _ptr(self.dom), _ptr(self.ratio), _ptr(self.err), _stream()))
+            d = self.dom
+            for cdt, mask in ((1, d == NEG), (2, d == POS), (3, (d == NEG) | (d == POS)), (4, d == IF), (5, (d == NEG) | (d == IF)),
+                              (6, (d == POS) | (d == IF)), (7, torch.ones_like(d, dtype=torch.bool))):
+                self.words[cdt] = BitArray.from_bool(mask).words
+            return self
         check(L.ngsx_classify(ctypes.byref(self.mesh.c_struct()), _ptr(lv), _ptr(self.words), _ptr(self.dom), _ptr(self.ratio),
                               _ptr(self.err), _stream()))
         if node_marks:
@@ -192,6 +199,17 @@ def IntegrateX(lset, mesh: Mesh, cf=None, order: int = 5, domain_type=IF, subdiv
     lv = _lset_vec(lset)
     out = torch.zeros(1, dtype=torch.float64, device=mesh.device)
     poly = _poly_of(cf)
+    if getattr(mesh, "tensor", False):                               # quadrilaterals / hexahedra (row f-5)
+        if quad_dir_policy != OPTIMAL:
+            raise NgsxError(-2, "quad_dir_policy FIRST / FALLBACK are outside the CUDA path (FIND_OPTIMAL, the reference's default, is)")
+        err = torch.zeros(2, dtype=torch.int64, device=mesh.device)
+        check(_lib_().ngsx_q_integrate(ctypes.byref(mesh.c_struct()), _ptr(lv), int(domain_type), order, ctypes.byref(poly), _ptr(out),
+                                       _ptr(err), _stream()))
+        if sync:
+            n, first = err.tolist()
+            if n:
+                raise NgsxError(-4, f"{n} element(s) carry a level set the reference's quadrilateral rule rejects (first: element {first})")
+        return float(out.item()) if sync else out
     defo = mesh.c_deformation()
     if defo is not None:                                             # mesh.SetDeformation(...): per-point geometry (row f-4)
         check(_lib_().ngsx_integrate_deformed(ctypes.byref(mesh.c_struct()), ctypes.byref(defo), _ptr(lv), int(domain_type), order,

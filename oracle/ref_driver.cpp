@@ -774,7 +774,7 @@ double ref_integrate_mesh(int dim, long ne, const int * el2v, const double * ver
 {
   int et = dim == 2 ? ET_TRIG : ET_TET;
   if (nthreads > 0) omp_set_num_threads(nthreads);
-  double sum = 0; long np = 0;
+  long double sum = 0; long np = 0;      // extended accumulator: the comparison should see the integrand, not 10^7 roundings of the checker
 #pragma omp parallel for schedule(static) reduction(+:sum,np)
   for (long e = 0; e < ne; e++)
     {
@@ -804,7 +804,7 @@ double ref_integrate_mesh(int dim, long ne, const int * el2v, const double * ver
       sum += lsum; np += n;
     }
   if (npts_total) *npts_total = np;
-  return sum;
+  return (double)sum;
 }
 
 // element matrices for a list of elements (els == nullptr: all), written densely elmats[k*nd*nd]; npts[k] = rule size or -1

@@ -1013,7 +1013,9 @@ def test_deformed_assemble_and_integrate(X, dim, dord):
         diff = abs(a.mat.to_scipy() - want)
         assert diff.max() <= RTOL * abs(want).max()
         want.sum_duplicates(); want.sort_indices()
-        wd = np.asarray(want[np.repeat(np.arange(Vh.ndof), np.diff(a.mat.rowptr.cpu().numpy())), a.mat.colidx.cpu().numpy()]).reshape(-1)
+        ri = np.repeat(np.arange(Vh.ndof), np.diff(a.mat.rowptr.cpu().numpy())).astype(np.int64).copy()
+        cj = np.array(a.mat.colidx.cpu().numpy(), dtype=np.int64, copy=True)
+        wd = np.asarray(want.tocsr()[ri, cj]).reshape(-1)
         assert_csr_close(a.mat.vals, wd, a.mat.rowptr)
         # (2) the same through the integrator's own deformation on the undeformed mesh
         mesh.UnsetDeformation()
@@ -1420,3 +1422,103 @@ def test_cut_buffer_grows_with_the_level_set(X):
     b += X.xfem.SymbolicBFI(levelset_domain={"levelset": gf, "domain_type": NEG}, form=form)
     b.Assemble()
     assert torch.equal(a.mat.vals, b.mat.vals)
+
+
+# ------------------------------------------------------------------------------------------------------------------
+# quadrilaterals / hexahedra (LevelsetCutQuadrilateral)
+# ------------------------------------------------------------------------------------------------------------------
+def _golden_split(g, key):
+    n = g[f"{key}_n"]
+    o = np.concatenate([[0], np.cumsum(np.maximum(n, 0))])
+    return n, o, g[f"{key}_pts"], g[f"{key}_wts"]
+
+
+@pytest.mark.parametrize("name,dim", [("quad", 2), ("hex", 3)])
+def test_quad_hex_rules_against_reference_golden(X, name, dim):
+    """the rules of the compiled reference's LevelsetCutQuadrilateral on the unit square / cube (tests/golden/quad_hex_rules.npz,
+    1 260 rules): point counts bit-exact, points to 1e-13, weights to 1e-11 relative (+ 1e-15: slivers at clamped vertices)"""
+    import os
+    g = np.load(os.path.join(os.path.dirname(__file__), "golden", "quad_hex_rules.npz"))
+    ls = g[f"{name}_lset"]
+    n, nv = ls.shape
+    corners = np.array([(0, 0), (1, 0), (1, 1), (0, 1)], dtype=np.float64) if dim == 2 else \
+        np.array([(0, 0, 0), (1, 0, 0), (1, 1, 0), (0, 1, 0), (0, 0, 1), (1, 0, 1), (1, 1, 1), (0, 1, 1)], dtype=np.float64)
+    vert = np.tile(corners, (n, 1))
+    el2v = np.arange(n * nv, dtype=np.int32).reshape(n, nv)
+    mesh = X.ngs.Mesh(X.meshes.TensorMesh(dim, torch.as_tensor(vert), torch.as_tensor(el2v)))
+    assert mesh.tensor and mesh.ne == n
+    lv = dev(ls.reshape(-1))
+    L = X.lib.load()
+    st = torch.cuda.current_stream().cuda_stream
+    err = torch.zeros(2, dtype=torch.int64, device="cuda")
+    for dt in (NEG, POS, IF):
+        for order in (1, 2, 4):
+            gn, go, gp, gw = _golden_split(g, f"{name}_dt{dt}_o{order}")
+            npts = torch.zeros(n, dtype=torch.int32, device="cuda")
+            X.lib.check(L.ngsx_q_rule_count(ctypes.byref(mesh.c_struct()), lv.data_ptr(), dt, order, npts.data_ptr(), err.data_ptr(), st))
+            assert err[0].item() == 0
+            assert np.array_equal(npts.cpu().numpy(), np.maximum(gn, 0)), (dt, order)
+            offs = torch.zeros(n + 1, dtype=torch.int64, device="cuda")
+            X.lib.check(L.ngsx_exclusive_scan(n, npts.data_ptr(), offs.data_ptr(), st))
+            total = int(offs[-1].item())
+            pts = torch.zeros((total, 3), dtype=torch.float64, device="cuda")
+            wts = torch.zeros(total, dtype=torch.float64, device="cuda")
+            X.lib.check(L.ngsx_q_rule_fill(ctypes.byref(mesh.c_struct()), lv.data_ptr(), dt, order, 0, offs.data_ptr(), pts.data_ptr(),
+                                           wts.data_ptr(), st))
+            assert np.abs(pts.cpu().numpy() - gp).max() <= 1e-13
+            w = wts.cpu().numpy()
+            assert (np.abs(w - gw) <= 1e-11 * np.abs(gw) + 1e-15).all(), (dt, order)
+    # CutInfo on the same cells: domains from the vertex signs, cut ratio = NEG part of the order-0 rules
+    gf = X.ngs.GridFunction(X.ngs.H1(mesh, order=1))
+    gf.vec.copy_(lv)
+    ci = X.xfem.CutInfo(mesh, gf)
+    haspos, hasneg = (ls > 0).any(axis=1), (ls < 0).any(axis=1)
+    want = np.where(haspos == hasneg, IF, np.where(hasneg, NEG, POS))
+    assert np.array_equal(ci.dom.cpu().numpy(), want)
+    assert np.array_equal(ci.GetElementsOfType(X.xfem.HASNEG).to_bool().cpu().numpy(), want != POS)
+    r = ci.ratio.cpu().numpy()
+    assert ((r[want == IF] > 0) & (r[want == IF] < 1)).all() and (r[want == NEG] == 1).all() and (r[want == POS] == 0).all()
+
+
+def test_quad_hex_reference_kats(X):
+    """known answers of tests/pytests/test_straightcutrule.py:105-285 on quadrilateral / hexahedral meshes"""
+    from math import sqrt
+    xf, ngs = X.xfem, X.ngs
+    x, y, z = ngs.x, ngs.y, ngs.z
+
+    def integ(mesh, lset, dt, order, cf=1.0):
+        gf = ngs.GridFunction(ngs.H1(mesh, order=1))
+        xf.InterpolateToP1(lset, gf)
+        return xf.Integrate(levelset_domain={"levelset": gf, "domain_type": dt}, cf=cf, mesh=mesh, order=order)
+
+    for N in (1, 10, 30):                                                    # :105-125
+        mesh = ngs.Mesh(X.meshes.MakeStructured2DMesh(nx=N, ny=N, quads=True))
+        for order in (2, 4, 8):
+            for dt, ref in ((NEG, 7 / 8), (POS, 1 / 8), (IF, 1 / sqrt(2))):
+                assert abs(integ(mesh, 1 - 2 * x - 2 * y, dt, order) - ref) < 5e-15 * (order + 1) ** 2 * max(1, N / 10)
+    m1 = ngs.Mesh(X.meshes.MakeStructured2DMesh(nx=1, ny=1, quads=True))
+    for eps in (1e-1, 1e-2, 5e-3, 1e-3, 0):                                  # :127-152
+        for ls in (1 - 2 * x + eps * (y - 0.5), 1 - 2 * y + eps * (x - 0.5)):
+            for dt, ref in ((NEG, 0.5), (POS, 0.5), (IF, sqrt(1 + eps * eps / 4))):
+                assert abs(integ(m1, ls, dt, 2) - ref) < 5e-15 * 9
+    for ls in (1 - 3 * x, 1 - 3 * y):                                        # :247-265
+        for dt, ref in ((NEG, 2 / 3), (POS, 1 / 3), (IF, 1.0)):
+            assert abs(integ(m1, ls, dt, 2) - ref) < 5e-15 * 9
+    h1 = ngs.Mesh(X.meshes.MakeStructured3DMesh(nx=1, ny=1, nz=1, hexes=True))
+    for order in (2, 4, 8):                                                  # :186-205
+        for dt, ref in ((POS, 1 / 48), (NEG, 47 / 48), (IF, sqrt(3) / 8)):
+            assert abs(integ(h1, 1 - 2 * x - 2 * y - 2 * z, dt, order) - ref) < 5e-15 * (order + 1) ** 2
+    for alpha in (0, 1, 2):                                                  # :207-238
+        val_pos = 2 ** (-alpha - 3) / (alpha ** 3 + 6 * alpha * alpha + 11 * alpha + 6)
+        for var in (x, y, z):
+            for dt, ref in ((POS, val_pos), (NEG, 1 / (alpha + 1) - val_pos)):
+                assert abs(integ(h1, 1 - 2 * x - 2 * y - 2 * z, dt, 4, cf=var ** alpha) - ref) < 5e-15 * 25
+    for var in (x, y, z):                                                    # :267-285
+        for dt, ref in ((POS, 0.5), (NEG, 0.5), (IF, 1.0)):
+            assert abs(integ(h1, 1 - 2 * var, dt, 2) - ref) < 5e-15 * 9
+    # a larger hexahedral mesh: the sphere's volume and area converge (curved interface, bilinear slices)
+    mesh = ngs.Mesh(X.meshes.MakeStructured3DMesh(24, hexes=True))
+    from math import pi
+    vol = integ(mesh, ngs.SphereLevelset((0.5, 0.5, 0.5), 0.35), NEG, 4)
+    area = integ(mesh, ngs.SphereLevelset((0.5, 0.5, 0.5), 0.35), IF, 4)
+    assert abs(vol - 4 / 3 * pi * 0.35 ** 3) < 2e-3 and abs(area - 4 * pi * 0.35 ** 2) < 1e-2
