@@ -666,7 +666,7 @@ class BilinearForm:
                 self.assembly = "colored"              # a CSR row longer than 256 entries: coloured scatter instead
                 return self._plan_for(k, integ)
         elif isinstance(integ, SymbolicCutBFI):
-            els = self._active_elements(integ)
+            els = self._listed_elements(integ).long()                  # independent of the level-set values: the kernel classifies
             table = fes.el2dof[els].contiguous()
             perm, cptr = color_list(table, fes.ndof, self.group_size)
             els_s = els[perm].to(torch.int32).contiguous()
@@ -716,10 +716,12 @@ class BilinearForm:
         only after it (ngsx_set_gather_wait_event), the geometry / quadrature stage before it overlaps the side work"""
         L = _lib_()
         fes = self.space
-        if self.mat is None or reallocate:
+        xver = getattr(getattr(fes, "x", None), "version", None)      # XFESpace.Update() changes the x-dofs: graph + plans are stale
+        if self.mat is None or reallocate or xver != self._graph_key:
             self._build_graph()
             self._plans.clear()
             self._xshared = None
+            self._graph_key = xver
         if fes.mesh.deformation is not None or any(getattr(i, "deformation", None) is not None for i in self.integrators):
             for integ in self.integrators:                         # what the deformed path covers (SURVEY section 8 row f-4)
                 if not isinstance(integ, SymbolicCutBFI) or integ.xterms is not None or self.assembly != "rows":
@@ -902,8 +904,8 @@ class LinearForm:
         self._h1 = space.std if self.compound else space
         self.integrators: List[SymbolicCutLFI] = []
         self.vec = torch.zeros(space.ndof, dtype=torch.float64, device=space.mesh.device)
-        self._plans: Dict[int, _Plan] = {}
-        self._xplans: Dict[int, tuple] = {}
+        self._xplans: Dict = {}          # ("h1", k): per-dof gather plan of integrator k; k: x-dof plans (tied to the XFESpace version)
+        self._xver = None
 
     def __iadd__(self, integ):
         if isinstance(integ, CutIntegrand):                            # f += form * dCut(...)
@@ -918,13 +920,40 @@ class LinearForm:
         self.integrators.append(integ)
         return self
 
+    def _listed_elements(self, integ) -> torch.Tensor:
+        """elements the integrator may ever touch (all, or definedonelements): independent of the level-set values, so the plan
+        survives a level-set update -- the kernels classify every listed element on every Assemble, like the reference's loop"""
+        mesh = self._h1.mesh
+        if integ.definedonelements is not None:
+            return torch.nonzero(integ.definedonelements.to_bool()).reshape(-1).to(torch.int32).contiguous()
+        return torch.arange(mesh.ne, dtype=torch.int32, device=mesh.device)
+
+    def _gather_plan(self, key, integ):
+        """per-dof gather plan of AddElementVector (NGS/comp/linearform.cpp:209-243 without atomics): for every dof the entries of
+        the flattened element vectors that belong to it, in (element, local dof) order"""
+        if key not in self._xplans:
+            fes = self._h1
+            els = self._listed_elements(integ)
+            n, nd = els.numel(), fes.nd
+            dof = fes.el2dof[els.long()].reshape(-1).long()
+            src = torch.arange(n * nd, device=dof.device)
+            order = torch.argsort(dof * max(n * nd, 1) + src)
+            dofptr = torch.zeros(fes.ndof + 1, dtype=torch.int64, device=dof.device)
+            dofptr[1:] = torch.cumsum(torch.bincount(dof, minlength=fes.ndof), 0)
+            self._xplans[key] = (els, dofptr, src[order].contiguous(), torch.empty((n, nd), dtype=torch.float64, device=dof.device))
+        return self._xplans[key]
+
     def Assemble(self):
-        """NGS/comp/linearform.cpp:209-243"""
+        """NGS/comp/linearform.cpp:209-243: element vectors of all listed elements (ngsx_elvec_h1 classifies them), then the
+        per-dof gather (ngsx_gather_vec: fixed order, no atomics, bitwise reproducible)"""
         L = _lib_()
         fes = self._h1
-        if self.vec.numel() != self.space.ndof:                            # XFESpace.Update changed the number of x-dofs
-            self.vec = torch.zeros(self.space.ndof, dtype=torch.float64, device=fes.mesh.device)
-            self._xplans.clear()
+        xver = getattr(getattr(self.space, "x", None), "version", None)
+        if self.vec.numel() != self.space.ndof or xver != self._xver:       # XFESpace.Update changed the x-dofs
+            if self.vec.numel() != self.space.ndof:
+                self.vec = torch.zeros(self.space.ndof, dtype=torch.float64, device=fes.mesh.device)
+            self._xplans = {k: v for k, v in self._xplans.items() if isinstance(k, tuple)}      # keep the H1 gather plans
+            self._xver = xver
         self.vec.zero_()
         for k, integ in enumerate(self.integrators):
             gfd = integ.deformation if getattr(integ, "deformation", None) is not None else fes.mesh.deformation
@@ -934,46 +963,23 @@ class LinearForm:
                 self._assemble_deformed(integ, k, gfd)
                 continue
             if integ.blocks[0] != 0.0:
-                if k not in self._plans:
-                    ci = CutInfo(fes.mesh, integ.lset)
-                    ba = ci.GetElementsOfType({NEG: HASNEG, POS: HASPOS, IF: CDOM_IF}[integ.dt])
-                    if integ.definedonelements is not None:
-                        ba = ba & integ.definedonelements
-                    els = ba.nonzero()
-                    table = fes.el2dof[els].contiguous()
-                    perm, cptr = color_list(table, fes.ndof, self.group_size)
-                    self._plans[k] = _Plan(els[perm].to(torch.int32).contiguous(), table[perm].contiguous(), cptr, self.group_size)
-                plan = self._plans[k]
-                poly = _poly_of(integ.coef)
-                check(L.ngsx_assemble_vec_h1(ctypes.byref(fes.mesh.c_struct()), _ptr(_lset_vec(integ.lset)), fes.order, integ.dt,
-                                             integ.intorder(fes.order), ctypes.byref(poly), plan.els.numel(), _ptr(plan.els), _ptr(plan.table),
-                                             plan.ncolors, plan.h_color_ptr, plan.group, _ptr(self.vec), _stream()))
+                els, dofptr, pairs, elvecs = self._gather_plan(("h1", k), integ)
+                if els.numel():
+                    poly = _poly_of(integ.coef)
+                    check(L.ngsx_elvec_h1(ctypes.byref(fes.mesh.c_struct()), _ptr(_lset_vec(integ.lset)), fes.order, integ.dt,
+                                          integ.intorder(fes.order), ctypes.byref(poly), els.numel(), _ptr(els), _ptr(elvecs), None, _stream()))
+                    check(L.ngsx_gather_vec(fes.ndof, _ptr(dofptr), _ptr(pairs), _ptr(elvecs), 1.0, 1, _ptr(self.vec), _stream()))
             if integ.has_x:
                 self._assemble_x(integ, k)
         return self
 
     def _assemble_deformed(self, integ, k, gfd):
-        """deformed mesh (row f-4): dense element vectors with per-point geometry (ngsx_elvec_h1_deformed), then the per-dof gather
-        of AddElementVector (ngsx_gather_vec: entries of a dof in (element, local dof) order, no atomics)"""
+        """deformed mesh (row f-4): dense element vectors with per-point geometry (ngsx_elvec_h1_deformed), then the per-dof gather"""
         L = _lib_()
         fes = self._h1
         if integ.blocks[0] == 0.0:
             return
-        key = ("def", k)
-        if key not in self._xplans:
-            ci = CutInfo(fes.mesh, integ.lset)
-            ba = ci.GetElementsOfType({NEG: HASNEG, POS: HASPOS, IF: CDOM_IF}[integ.dt])
-            if integ.definedonelements is not None:
-                ba = ba & integ.definedonelements
-            els = ba.nonzero().to(torch.int32).contiguous()
-            n, nd = els.numel(), fes.nd
-            dof = fes.el2dof[els.long()].reshape(-1).long()
-            src = torch.arange(n * nd, device=dof.device)
-            order = torch.argsort(dof * max(n * nd, 1) + src)
-            dofptr = torch.zeros(fes.ndof + 1, dtype=torch.int64, device=dof.device)
-            dofptr[1:] = torch.cumsum(torch.bincount(dof, minlength=fes.ndof), 0)
-            self._xplans[key] = (els, dofptr, src[order].contiguous(), torch.empty((n, nd), dtype=torch.float64, device=dof.device))
-        els, dofptr, pairs, elvecs = self._xplans[key]
+        els, dofptr, pairs, elvecs = self._gather_plan(("h1", k), integ)
         if els.numel() == 0:
             return
         poly = _poly_of(integ.coef)

@@ -104,6 +104,7 @@ class XFESpace(_FESpaceBase):
         self.el2dofs = self.basedof2xdof[base.el2dof[self.if_els.long()].long()].contiguous()          # [nIF][nd] (:323-331)
         self.xsign = self.domofdof[self.el2dofs.long()].contiguous()                                   # GetDomainNrs per IF element
         self._elpos = None
+        self.version = getattr(self, "version", 0) + 1      # forms compare it and rebuild what they derived from the cut state
         return self
 
     def GetCutInfo(self):

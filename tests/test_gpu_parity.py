@@ -235,7 +235,7 @@ def test_assemble_csr_against_oracle(X, dim, nx, fo, dt, mode, group):
     vals, nass = orc.assemble_csr(dim, el2v, vert, ls, fo, Vh.el2dof.cpu().numpy(), dt, a.integrators[0].intorder(fo), 1.3, 0.7,
                                   np.array([0, mesh.ne]), els, a.mat.rowptr.cpu().numpy(), a.mat.colidx.cpu().numpy(), nthreads=1)
     if mode == "colored":
-        assert nass == a._plans[0].els.numel()
+        assert a._plans[0].els.numel() == mesh.ne                              # level-set independent list: the kernel classifies
     assert_csr_close(a.mat.vals, vals, a.mat.rowptr)
     # the sparsity is the full element graph: same pattern as scipy's from the dof table
     import scipy.sparse as sp
@@ -1522,3 +1522,81 @@ def test_quad_hex_reference_kats(X):
     vol = integ(mesh, ngs.SphereLevelset((0.5, 0.5, 0.5), 0.35), NEG, 4)
     area = integ(mesh, ngs.SphereLevelset((0.5, 0.5, 0.5), 0.35), IF, 4)
     assert abs(vol - 4 / 3 * pi * 0.35 ** 3) < 2e-3 and abs(area - 4 * pi * 0.35 ** 2) < 1e-2
+
+
+def test_plans_survive_a_moving_level_set(X):
+    """a form assembled, the level set moved, the SAME form assembled again == a fresh form (the reference loops over all
+    elements on every Assemble): LinearForm (affine + deformed), coloured and row-gather BilinearForm, and the compound
+    [Vh, XFESpace] forms after XFESpace.Update()"""
+    xf, ngs = X.xfem, X.ngs
+    mesh = ngs.Mesh(X.meshes.MakeStructured3DMesh(7))
+    gf = ngs.GridFunction(ngs.H1(mesh, order=1))
+    ls_a, ls_b = ngs.SphereLevelset((0.5, 0.5, 0.5), 0.25), ngs.SphereLevelset((0.45, 0.55, 0.5), 0.41)
+    Vh = ngs.H1(mesh, order=2)
+    u, v = Vh.TnT()
+    x, y = ngs.x, ngs.y
+    Vd = ngs.H1(mesh, order=1, dim=3)
+    defo = ngs.GridFunction(Vd)
+    defo.vec.copy_(dev(0.01 * np.random.default_rng(1).uniform(-1, 1, (Vd.ndof, 3))))
+
+    def forms():
+        out = []
+        for dt in (NEG, IF):
+            f = xf.LinearForm(Vh)
+            f += xf.SymbolicLFI(levelset_domain={"levelset": gf, "domain_type": dt}, form=(1.0 + x * y) * v)
+            g = xf.LinearForm(Vh)
+            g += xf.SymbolicLFI(levelset_domain={"levelset": gf, "domain_type": dt}, form=(1.0 + x * y) * v, deformation=defo)
+            out += [f, g]
+            for mode in ("rows", "colored"):
+                a = xf.BilinearForm(Vh)
+                a.assembly = mode
+                a += xf.SymbolicBFI(levelset_domain={"levelset": gf, "domain_type": dt}, form=ngs.grad(u) * ngs.grad(v) + u * v)
+                out.append(a)
+        return out
+
+    xf.InterpolateToP1(ls_a, gf)
+    old = forms()
+    for o in old:
+        o.Assemble()
+    xf.InterpolateToP1(ls_b, gf)
+    fresh = forms()
+    for o, n in zip(old, fresh):
+        o.Assemble()
+        if hasattr(o, "check_degenerate"):
+            try:
+                o.check_degenerate()
+            except X.lib.NgsxError as exc:                                        # the cut buffer grew: assemble again
+                assert exc.status == -5
+                o.Assemble()
+                o.check_degenerate()
+        n.Assemble()
+        a, b = (o.vec, n.vec) if hasattr(o, "vec") else (o.mat.vals, n.mat.vals)
+        assert torch.equal(a, b)
+    # compound space: XFESpace.Update() after the level set moved
+    from ngsxfem_b200.xfes import FESpace
+    xf.InterpolateToP1(ls_a, gf)
+    ci = xf.CutInfo(mesh, gf)
+    Vhx = xf.XFESpace(Vh, ci)
+    VhG = FESpace([Vh, Vhx])
+    (u_std, u_x), (v_std, v_x) = VhG.TrialFunction(), VhG.TestFunction()
+
+    def xforms():
+        a = xf.BilinearForm(VhG)
+        a += xf.SymbolicBFI(levelset_domain={"levelset": gf, "domain_type": NEG},
+                            form=(ngs.grad(u_std) + xf.neg_grad(u_x)) * (ngs.grad(v_std) + xf.neg_grad(v_x)))
+        a += xf.SymbolicBFI(levelset_domain={"levelset": gf, "domain_type": IF}, form=(u_std + xf.neg(u_x)) * (v_std + xf.neg(v_x)))
+        f = xf.LinearForm(VhG)
+        f += xf.SymbolicLFI(levelset_domain={"levelset": gf, "domain_type": NEG}, form=(1.0 + x) * (v_std + xf.neg(v_x)))
+        return a, f
+    a0, f0 = xforms()
+    a0.Assemble(); f0.Assemble()
+    n0 = VhG.ndof
+    xf.InterpolateToP1(ls_b, gf)
+    ci.Update(gf)
+    Vhx.Update()
+    assert VhG.ndof != n0
+    a0.Assemble(); f0.Assemble()
+    a1, f1 = xforms()
+    a1.Assemble(); f1.Assemble()
+    assert torch.equal(a0.mat.rowptr, a1.mat.rowptr) and torch.equal(a0.mat.colidx, a1.mat.colidx)
+    assert torch.equal(a0.mat.vals, a1.mat.vals) and torch.equal(f0.vec, f1.vec)
