@@ -146,7 +146,8 @@ __global__ void __launch_bounds__(128) k_fp_table(int64_t npatch, const int32_t 
 template <int DIM, int ORDER>
 __global__ void __launch_bounds__(FP_WARPS * 32) k_facetpatch_c(ngsx_mesh M, const double4 *__restrict__ rule, int nr, double coef, int hpow,
                                                                int64_t npatch, const int32_t *__restrict__ patch_els,
-                                                               const uint8_t *__restrict__ cidx, double *__restrict__ mats) {
+                                                               const uint8_t *__restrict__ cidx, double *__restrict__ mats,
+                                                               const int32_t *__restrict__ rowslot) {
   constexpr int ND = H1<DIM, ORDER>::ND, NFD = DIM == 2 ? (ORDER == 1 ? 2 : 3) : (ORDER == 1 ? 3 : 6);   // dofs on the shared facet
   constexpr int NP = 2 * ND - NFD, NE = NP * NP, NS = NP * (NP + 1) / 2, T = (NS + 31) / 32;   // symmetric: upper triangle only
   extern __shared__ __align__(16) unsigned char smem_raw[];
@@ -232,8 +233,15 @@ __global__ void __launch_bounds__(FP_WARPS * 32) k_facetpatch_c(ngsx_mesh M, con
 #pragma unroll
     for (int t = 0; t < T; t++) {
       if (lane + 32 * t < NS) {
-        mats[k * NE + ei[t] * NP + ej[t]] = acc[t];
-        mats[k * NE + ej[t] * NP + ei[t]] = acc[t];
+        if (rowslot) {                                            // packed rows: row i of block k at the slot of the pair (k, i)
+          constexpr int NPP = NP + (NP & 1);
+          const int si = __ldg(rowslot + k * NP + ei[t]), sj = __ldg(rowslot + k * NP + ej[t]);
+          if (si >= 0) mats[(int64_t)si * NPP + ej[t]] = acc[t];
+          if (sj >= 0) mats[(int64_t)sj * NPP + ei[t]] = acc[t];
+        } else {
+          mats[k * NE + ei[t] * NP + ej[t]] = acc[t];
+          mats[k * NE + ej[t] * NP + ei[t]] = acc[t];
+        }
       }
     }
   }
@@ -241,7 +249,7 @@ __global__ void __launch_bounds__(FP_WARPS * 32) k_facetpatch_c(ngsx_mesh M, con
 
 template <int DIM, int ORDER>
 static int launch_fpc(const ngsx_mesh &M, const DeviceData *dd, const double4 *rule, int nr, double coef, int hpow, int64_t np,
-                      const int32_t *patch_els, const uint8_t *cidx, int ndp, double *mats, cudaStream_t st) {
+                      const int32_t *patch_els, const uint8_t *cidx, int ndp, double *mats, const int32_t *rowslot, cudaStream_t st) {
   constexpr int ND = H1<DIM, ORDER>::ND, NFD = DIM == 2 ? (ORDER == 1 ? 2 : 3) : (ORDER == 1 ? 3 : 6), NP = 2 * ND - NFD;
   if (ndp != NP) { set_error("facetpatch_cmat: ndp does not match the merged dof count of this element type"); return NGSX_ERR_ARG; }
   size_t smem = (size_t)nr * 32 + (size_t)FP_WARPS * (32 * NP + 32) * 8;
@@ -249,7 +257,7 @@ static int launch_fpc(const ngsx_mesh &M, const DeviceData *dd, const double4 *r
   NGSX_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   int64_t need = (np + FP_WARPS - 1) / FP_WARPS;
   unsigned grid = (unsigned)std::max<int64_t>(1, std::min<int64_t>(need, (int64_t)dd->sm_count * 8));
-  kern<<<grid, FP_WARPS * 32, smem, st>>>(M, rule, nr, coef, hpow, np, patch_els, cidx, mats);
+  kern<<<grid, FP_WARPS * 32, smem, st>>>(M, rule, nr, coef, hpow, np, patch_els, cidx, mats, rowslot);
   NGSX_LAUNCH_CHECK();
   return NGSX_OK;
 }
@@ -307,14 +315,14 @@ extern "C" int ngsx_facetpatch_cmat_h1(const ngsx_mesh *mesh, int fe_order, doub
   if (!dd) return NGSX_ERR_CUDA;
   const double4 *rule; int nr;
   if (!rule_lookup(dd, mesh->dim, 2 * fe_order, &rule, &nr)) { set_error("facetpatch_cmat: rule not tabulated"); return NGSX_ERR_UNSUPPORTED; }
-  if (take_packed_output()) { set_error("packed output is not served by this entry point yet"); return NGSX_ERR_UNSUPPORTED; }
+  const int32_t *rowslot = take_packed_output();
   if (npatch == 0) return NGSX_OK;
   cudaStream_t st = as_stream(stream);
   switch (mesh->dim * 10 + fe_order) {
-    case 21: return launch_fpc<2, 1>(*mesh, dd, rule, nr, coef, hpow, npatch, patch_els, cidx, ndp, mats, st);
-    case 22: return launch_fpc<2, 2>(*mesh, dd, rule, nr, coef, hpow, npatch, patch_els, cidx, ndp, mats, st);
-    case 31: return launch_fpc<3, 1>(*mesh, dd, rule, nr, coef, hpow, npatch, patch_els, cidx, ndp, mats, st);
-    case 32: return launch_fpc<3, 2>(*mesh, dd, rule, nr, coef, hpow, npatch, patch_els, cidx, ndp, mats, st);
+    case 21: return launch_fpc<2, 1>(*mesh, dd, rule, nr, coef, hpow, npatch, patch_els, cidx, ndp, mats, rowslot, st);
+    case 22: return launch_fpc<2, 2>(*mesh, dd, rule, nr, coef, hpow, npatch, patch_els, cidx, ndp, mats, rowslot, st);
+    case 31: return launch_fpc<3, 1>(*mesh, dd, rule, nr, coef, hpow, npatch, patch_els, cidx, ndp, mats, rowslot, st);
+    case 32: return launch_fpc<3, 2>(*mesh, dd, rule, nr, coef, hpow, npatch, patch_els, cidx, ndp, mats, rowslot, st);
   }
   return NGSX_ERR_UNSUPPORTED;
 }

@@ -130,7 +130,8 @@ template <int DIM, int ORDER>
 __global__ void __launch_bounds__(XMT) k_xfem_mom(ngsx_mesh M, const double *__restrict__ lset, const CutTable *__restrict__ tab, int dt,
                                                  const double4 *__restrict__ rule_vol, int nr_vol, const double4 *__restrict__ rule_if, int nr_if,
                                                  XTermsDev X, int64_t nlist, const int32_t *__restrict__ els, const int8_t *__restrict__ xsign,
-                                                 const double *__restrict__ ratio, int accumulate, double *__restrict__ mats) {
+                                                 const double *__restrict__ ratio, int accumulate, double *__restrict__ mats,
+                                                 const int32_t *__restrict__ rowslot) {
   using XM = XMom<DIM, ORDER>;
   constexpr int ND = XM::ND, NV = XM::NV, NEDGE = XM::NEDGE, N2C = 2 * ND;
   extern __shared__ __align__(16) unsigned char xsmem[];
@@ -306,6 +307,13 @@ __global__ void __launch_bounds__(XMT) k_xfem_mom(ngsx_mesh M, const double *__r
     double *out = mats + k * (N2C * N2C);
 #pragma unroll 1
     for (int i = 0; i < ND; i++) {
+      // packed rows (ngsx_set_packed_output): rows i and ND + i of block k go to the slots of their pairs (N2C is even)
+      double *orow[2] = {out + i * N2C, out + (ND + i) * N2C};
+      if (rowslot) {
+        const int s0 = __ldg(rowslot + k * N2C + i), s1 = __ldg(rowslot + k * N2C + ND + i);
+        orow[0] = s0 >= 0 ? mats + (int64_t)s0 * N2C : nullptr;
+        orow[1] = s1 >= 0 ? mats + (int64_t)s1 * N2C : nullptr;
+      }
       const int ci = 1 + (int)__ldg(sg + i);                            // block class of the x copy of dof i (1 + its sign)
 #pragma unroll 1
       for (int j = 0; j < ND; j++) {
@@ -321,8 +329,10 @@ __global__ void __launch_bounds__(XMT) k_xfem_mom(ngsx_mesh M, const double *__r
             const double *cf = coefs + c * 5;
             double v = cf[0] * b0;
             v = fma(cf[1], b1, v); v = fma(cf[2], b2, v); v = fma(cf[3], b3, v); v = fma(cf[4], b4, v);
-            double *o = out + (bI * ND + i) * N2C + bJ * ND + j;
-            *o = accumulate ? *o + v : v;
+            if (orow[bI]) {
+              double *o = orow[bI] + bJ * ND + j;
+              *o = accumulate ? *o + v : v;
+            }
           }
       }
     }
@@ -331,7 +341,7 @@ __global__ void __launch_bounds__(XMT) k_xfem_mom(ngsx_mesh M, const double *__r
 
 template <int DIM, int ORDER>
 static int launch_xfem(const ngsx_mesh &M, const double *lset, const DeviceData *dd, int dt, const double4 *rv, int nv, const double4 *ri, int ni,
-                       const XTermsDev &X, int64_t nlist, const int32_t *els, const int8_t *xsign, const double *ratio, int accumulate, double *mats,
+                       const XTermsDev &X, int64_t nlist, const int32_t *els, const int8_t *xsign, const double *ratio, int accumulate, double *mats, const int32_t *rowslot,
                        cudaStream_t st) {
   const size_t smem = (size_t)(nv + ni) * sizeof(double4) + 16 * sizeof(CutEntry) + (size_t)XMT * (XCO + XMom<DIM, ORDER>::TOT) * sizeof(double);
   auto kern = k_xfem_mom<DIM, ORDER>;
@@ -341,7 +351,7 @@ static int launch_xfem(const ngsx_mesh &M, const double *lset, const DeviceData 
   if (occ < 1) { set_error("xfem_elmat: kernel does not fit on an SM"); return NGSX_ERR_CUDA; }
   const int64_t need = (nlist + XMT - 1) / XMT;
   const unsigned grid = (unsigned)std::max<int64_t>(1, std::min<int64_t>(need, (int64_t)dd->sm_count * occ));
-  kern<<<grid, XMT, smem, st>>>(M, lset, dd->cut_table, dt, rv, nv, ri, ni, X, nlist, els, xsign, ratio, accumulate, mats);
+  kern<<<grid, XMT, smem, st>>>(M, lset, dd->cut_table, dt, rv, nv, ri, ni, X, nlist, els, xsign, ratio, accumulate, mats, rowslot);
   NGSX_LAUNCH_CHECK();
   return NGSX_OK;
 }
@@ -388,14 +398,14 @@ extern "C" int ngsx_xfem_elmat_h1(const ngsx_mesh *mesh, const double *lset_v, i
     }
     X.cls[9] = (int8_t)o;
   }
-  if (take_packed_output()) { set_error("packed output is not served by this entry point yet"); return NGSX_ERR_UNSUPPORTED; }
+  const int32_t *rowslot = take_packed_output();
   if (nlist == 0) return NGSX_OK;
   cudaStream_t st = as_stream(stream);
   switch (mesh->dim * 10 + fe_order) {
-    case 21: return launch_xfem<2, 1>(*mesh, lset_v, dd, dt, rv, nv, ri, ni, X, nlist, els, xsign, ratio, accumulate, mats, st);
-    case 22: return launch_xfem<2, 2>(*mesh, lset_v, dd, dt, rv, nv, ri, ni, X, nlist, els, xsign, ratio, accumulate, mats, st);
-    case 31: return launch_xfem<3, 1>(*mesh, lset_v, dd, dt, rv, nv, ri, ni, X, nlist, els, xsign, ratio, accumulate, mats, st);
-    case 32: return launch_xfem<3, 2>(*mesh, lset_v, dd, dt, rv, nv, ri, ni, X, nlist, els, xsign, ratio, accumulate, mats, st);
+    case 21: return launch_xfem<2, 1>(*mesh, lset_v, dd, dt, rv, nv, ri, ni, X, nlist, els, xsign, ratio, accumulate, mats, rowslot, st);
+    case 22: return launch_xfem<2, 2>(*mesh, lset_v, dd, dt, rv, nv, ri, ni, X, nlist, els, xsign, ratio, accumulate, mats, rowslot, st);
+    case 31: return launch_xfem<3, 1>(*mesh, lset_v, dd, dt, rv, nv, ri, ni, X, nlist, els, xsign, ratio, accumulate, mats, rowslot, st);
+    case 32: return launch_xfem<3, 2>(*mesh, lset_v, dd, dt, rv, nv, ri, ni, X, nlist, els, xsign, ratio, accumulate, mats, rowslot, st);
   }
   return NGSX_ERR_UNSUPPORTED;
 }

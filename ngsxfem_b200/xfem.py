@@ -629,7 +629,7 @@ class BilinearForm:
             info = (ctypes.c_int64 * 6)()
             check(L.ngsx_rowplan_info(h, info))
             shared = _RowPlan(fes.x.if_els, ctab, h, tuple(info))
-            shared.mats = torch.empty((ctab.shape[0], ctab.shape[1] ** 2), dtype=torch.float64, device=fes.mesh.device)
+            shared.slots, shared.mats = _packed_rows(shared, ctab.shape[1])     # packed rows of the compound blocks (2 nd is even)
             self._xshared = shared
         from . import xfes
         plan_b = _XPlan(self._xshared, xfes.make_xterms(integ.xterms), plan_a)
@@ -707,7 +707,6 @@ class BilinearForm:
         check(L.ngsx_rowplan_info(h, info))
         plan = _RowPlan(pe, table, h, tuple(info))
         plan.cidx, plan.ndp = cidx, ndp
-        plan.mats = torch.empty((npatch, ndp * ndp), dtype=torch.float64, device=mesh.device)
         return plan
 
     def Assemble(self, reallocate: bool = False, gather_after=None):
@@ -784,7 +783,7 @@ class BilinearForm:
                                              plan.els.numel(), _ptr(plan.els), _ptr(plan.slots), plan.ncolors, plan.h_color_ptr,
                                              plan.group, _ptr(self.mat.vals), _stream()))
         if x_blocks:                                               # one gather for the summed blocks of all compound integrators
-            check(L.ngsx_assemble_csr_rows_mats(self._xshared.handle, _ptr(self._xshared.mats), 1, _ptr(self.mat.vals), _stream()))
+            check(L.ngsx_assemble_csr_rows_packed(self._xshared.handle, _ptr(self._xshared.mats), 1, _ptr(self.mat.vals), _stream()))
         return self
 
     def _deformation_of(self, integ):
@@ -842,6 +841,7 @@ class BilinearForm:
             self._err_armed = True
         n = plan.els.numel()
         if n:
+            L.ngsx_set_packed_output(plan.shared.slots)
             check(L.ngsx_xfem_elmat_h1(mesh_c, _ptr(lv), h1.order, integ.dt, io, len(integ.xterms), plan.xterms, n, _ptr(plan.els),
                                        _ptr(fes.x.xsign), _ptr(fes.x.cutinfo.ratio), 1 if x_blocks else 0, _ptr(plan.mats), _stream()))
             return 1
@@ -855,9 +855,11 @@ class BilinearForm:
         npatch = plan.els.shape[0]
         if npatch == 0:
             return
+        slots, rows = _packed_rows(plan, plan.ndp)                     # the kernel writes block rows where the gather's schedule reads them
+        L.ngsx_set_packed_output(slots)
         check(L.ngsx_facetpatch_cmat_h1(ctypes.byref(fes.mesh.c_struct()), fes.order, integ.coef, integ.hpow, npatch,
-                                        _ptr(plan.els), _ptr(plan.cidx), plan.ndp, _ptr(plan.mats), _stream()))
-        check(L.ngsx_assemble_csr_rows_mats(plan.handle, _ptr(plan.mats), 1, _ptr(self.mat.vals), _stream()))
+                                        _ptr(plan.els), _ptr(plan.cidx), plan.ndp, _ptr(rows), _stream()))
+        check(L.ngsx_assemble_csr_rows_packed(plan.handle, _ptr(rows), 1, _ptr(self.mat.vals), _stream()))
 
     def elmats(self, k: int = 0):
         """dense element matrices of integrator k for its active elements (the per-element view CalcElementMatrixAdd would serve)"""

@@ -374,8 +374,11 @@ def test_ghost_penalty_row_gather(X, dim, fo):
     plan = a._plans[1]
     el2v, vert, e2d, ls = mesh.el2v.cpu().numpy(), mesh.vert.cpu().numpy(), Vh.el2dof.cpu().numpy(), gf.vec.cpu().numpy()
     # merged blocks vs the oracle
-    pe, tab, mats = plan.els.cpu().numpy(), plan.table.cpu().numpy(), plan.mats.cpu().numpy()
     ndp = plan.ndp
+    dmats = torch.empty((plan.els.shape[0], ndp * ndp), dtype=torch.float64, device="cuda")      # dense merged blocks (Assemble uses packed rows)
+    X.lib.check(X.lib.load().ngsx_facetpatch_cmat_h1(ctypes.byref(mesh.c_struct()), fo, 0.1, -2, plan.els.shape[0], plan.els.data_ptr(),
+                                                     plan.cidx.data_ptr(), ndp, dmats.data_ptr(), torch.cuda.current_stream().cuda_stream))
+    pe, tab, mats = plan.els.cpu().numpy(), plan.table.cpu().numpy(), dmats.cpu().numpy()
     assert len(pe) == int(np.count_nonzero(ba.to_bool().cpu().numpy() & (mesh.facets()[1][:, 1] >= 0).cpu().numpy()))
     A = sp.lil_matrix((Vh.ndof, Vh.ndof))
     for k, (e0, e1) in enumerate(pe):
