@@ -433,11 +433,15 @@ def run_b200(args):
     # units of this rank's launches: element matrices scattered = (row, element) pairs / dofs per element (== listed elements at N=1)
     n_units = plan.npairs / P["Vh"].nd if hasattr(plan, "npairs") else n_local
     achieved = ALGO_BYTES_SCATTER * n_units / (rows_ms * 1e-3) / 1e9
-    stage_achieved = ALGO_BYTES_PER_ELEMENT * n_units / (as_local * 1e-3) / 1e9
+    # the assemble stage against the full survey figure: SERIAL sum of its kernels, each timed alone (the live interval of the
+    # stage contains the gather's wait for the sweeps on the side streams)
+    ks = (serial_break or {}).get("kernel_ms") or ({"k_geom": geom_ms, "k_cutmat": cut_ms, "k_rows": rows_ms} if geom_ms is not None else None)
+    stage_serial_ms = sum(ks.values()) if ks else as_local
+    stage_achieved = ALGO_BYTES_PER_ELEMENT * n_units / (stage_serial_ms * 1e-3) / 1e9
     info = getattr(plan, "npairs", None)
-    own_bytes = (8 * plan.nnz_covered + 16 * plan.npairs + 64 * n_local) if info is not None else None   # values written once + descriptors + factors
+    own_bytes = (8 * plan.nnz_covered + 16 * plan.npairs + 128 * n_local) if info is not None else None   # values written once + descriptors + geometry records
     traffic = None
-    tp = os.path.join(ROOT, "profiles", "r01_rows_traffic.json")
+    tp = os.path.join(ROOT, "profiles", "r02_rows_traffic.json")
     if os.path.exists(tp):
         traffic = json.load(open(tp)).get("dram_bytes_per_launch")
     out = {
@@ -453,17 +457,21 @@ def run_b200(args):
                                                                      "with": "the three sweeps on three streams beside the whole assembly chain"}[order_default],
                    "l2": "inputs larger than L2 (CSR values + pair descriptors + mesh > 1.4 GB touched per step vs 126 MB L2); no explicit flush",
                    "partition": "owner-computes: contiguous chunks of equal cost (cut element = 3.2 uncut) of the HASNEG element list per rank, a CSR row belongs to the rank of the first listed element touching it, halo elements re-evaluated, no interface-row exchange; element blocks for Integrate, scalars all-reduced (NCCL)"},
-        "roofline": {"bound": "hbm", "kernel": "k_rows<10,6> (owner-computes row gather: every CSR value of the assembled operator written once)",
+        "roofline": {"bound": "hbm", "kernel": "k_rows<3,2> (owner-computes row gather: every CSR value of the assembled operator written once)",
                      "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": traffic,
                      "peak_source": peak_src, "algorithmic_bytes_per_element": ALGO_BYTES_SCATTER,
                      "kernel_ms": {"k_geom": geom_ms, "k_cutmat": cut_ms, "k_rows": rows_ms},
                      "kernel_ms_note": ("live in the timed region; with the sweeps beside them k_geom / k_cutmat share the SMs and the k_cutmat interval "
                                         "ends after the gather's wait for the sweeps (config.stage_ms_one_stream.kernel_ms has them alone); k_rows runs alone")
                                        if (not serial and order_default == "join") else "live in the timed region",
-                     "assemble_stage": {"achieved": stage_achieved, "frac": stage_achieved / peak, "algorithmic_bytes_per_element": ALGO_BYTES_PER_ELEMENT},
+                     "assemble_stage": {"achieved": stage_achieved, "frac": stage_achieved / peak, "algorithmic_bytes_per_element": ALGO_BYTES_PER_ELEMENT,
+                                        "ms_serial_kernel_sum": stage_serial_ms, "kernel_ms_alone": ks},
+                     "dram": None if traffic is None else {"bytes_per_launch": traffic, "achieved": traffic / (rows_ms * 1e-3) / 1e9,
+                                                           "frac": traffic / (rows_ms * 1e-3) / 1e9 / peak,
+                                                           "note": "dram__bytes_read.sum + dram__bytes_write.sum of the ncu --set full capture (profiles/) over the live kernel time"},
                      "own_algorithm": None if own_bytes is None else {"bytes_per_launch": own_bytes, "achieved": own_bytes / (rows_ms * 1e-3) / 1e9,
                                                                     "frac": own_bytes / (rows_ms * 1e-3) / 1e9 / peak,
-                                                                    "note": "minimum traffic of the gather formulation: 8 B per CSR value + 16 B per (row, element) pair + 64 B factors per element"},
+                                                                    "note": "minimum traffic of the gather formulation: 8 B per CSR value + 16 B per (row, element) pair + 128 B geometry records per element"},
                      "classify_gbs": ALGO_BYTES_CLASSIFY * mesh.ne / (cl_ms * 1e-3) / 1e9},
         "e2e": {"value": n_global / (e2e_ms / args.steps * 1e-3), "unit": "elements/s", "h2d_bytes_per_step": int(h_lset.numel() * 8),
                 "d2h_bytes_per_step": int(h_vals[0].numel() * 8 + 16 + h_err[0].numel() * 8), "ms_per_step": e2e_ms / args.steps,

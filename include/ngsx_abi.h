@@ -21,8 +21,9 @@
  *   ngsx_integrate            cutint/python_cutint.cpp:20-72        (IntegrateX)
  *   ngsx_st_rule_count/_fill, ngsx_st_integrate
  *                             cutint/spacetimecutrule.cpp:6-196, cutint/xintegration.cpp:38-58 (time_order >= 0)
- *   ngsx_facets_neighbor_types, ngsx_elements_with_neighbor_facets, ngsx_dofs_of_elements
- *                             xfem/cutinfo.cpp:191-304              (xfem/python_xfem.cpp:168-318)
+ *   ngsx_facets_neighbor_types[_periodic], ngsx_elements_with_neighbor_facets, ngsx_dofs_of_elements
+ *                             xfem/cutinfo.cpp:191-329              (xfem/python_xfem.cpp:168-318; GetDofsOfFacets = ngsx_dofs_of_elements
+ *                                                                    on the facet -> dof table)
  *   ngsx_facetpatch_elmat_h1, ngsx_facetpatch_cmat_h1
  *                             xfem/symboliccutbfi.cpp:1115-1411     (CalcFacetMatrix, xfem/symboliccutbfi.hpp:253-259)
  *   ngsx_xfem_elmat_h1        xfem/xfemdiffops.cpp:8-66 + xfem/symboliccutbfi.cpp:73-315 (compound [Vh, XFESpace] element)
@@ -112,6 +113,10 @@ int ngsx_interpolate_p1_cf(const ngsx_mesh *mesh, int kind, const double *h_para
  * Degenerate elements (the reference throws) are counted in err and get dom = -1, no bits. */
 int ngsx_classify(const ngsx_mesh *mesh, const double *lset_v, uint32_t *cdom_words, int8_t *dom, double *ratio,
                   int64_t *err, void *stream);
+/* the BND pass of CutInformation::Update (xfem/cutinfo.cpp:47, 67: `for (VorB vb : {VOL, BND})`): boundary elements of a mesh
+ * of dimension dim (segments / triangles), bnd_el2v [nbe][dim]; outputs as ngsx_classify */
+int ngsx_classify_bnd(int dim, int64_t nbe, const int32_t *bnd_el2v, const double *lset_v, uint32_t *cdom_words, int8_t *dom,
+                      double *ratio, int64_t *err, void *stream);
 /* cut_neighboring_node / dom_of_node for one node type (xfem/cutinfo.cpp:122-186): el2node [ne][npe];
  * cut_nb_words [(nnodes+31)/32] is OR-ed (must be zeroed by the caller), dom_of_node [nnodes] int32 must be pre-filled
  * with IF(2); it is lowered with an integer atomicMin (NEG < POS < IF), which makes the reference's racy last-writer
@@ -309,6 +314,11 @@ int ngsx_q_integrate(const ngsx_mesh *mesh, const double *lset_v, int dt, int or
 /* facet2el [nf][2], -1 = no neighbour (boundary facet: bnd_val_a/b are used, xfem/cutinfo.cpp:238-241) */
 int ngsx_facets_neighbor_types(int64_t nf, const int32_t *facet2el, const uint32_t *a_words, const uint32_t *b_words,
                                int bnd_val_a, int bnd_val_b, int use_and, uint32_t *out_words, void *stream);
+/* the same on a mesh with periodic identifications (xfem/cutinfo.cpp:225-236): periodic_facet [nf] = MeshAccess::GetPeriodicFacet
+ * (the partner facet, or the facet itself / -1 where there is none); a boundary facet with a partner of larger number takes the
+ * partner's element as its second neighbour, the partner itself stays unmarked */
+int ngsx_facets_neighbor_types_periodic(int64_t nf, const int32_t *facet2el, const int32_t *periodic_facet, const uint32_t *a_words,
+                                        const uint32_t *b_words, int bnd_val_a, int bnd_val_b, int use_and, uint32_t *out_words, void *stream);
 int ngsx_elements_with_neighbor_facets(int64_t nf, const int32_t *facet2el, const uint32_t *facet_words,
                                        int64_t ne, uint32_t *out_words /* zeroed by the callee */, void *stream);
 int ngsx_dofs_of_elements(int64_t n, int32_t nd, const int32_t *table, const uint32_t *a_words,

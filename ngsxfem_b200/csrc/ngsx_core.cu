@@ -357,6 +357,39 @@ __global__ void __launch_bounds__(256) k_classify_cut(ngsx_mesh M, const double 
   }
 }
 
+// boundary elements of a 2D mesh: segments.  Sign test as everywhere; cut ratio = NEG part of the unit segment (the order-0
+// rules of xfem/cutinfo.cpp:79-91 on ET_SEGM: the level set is linear, the zero at phi_0 / (phi_0 - phi_1) from vertex 0)
+__global__ void __launch_bounds__(256) k_classify_segm(int64_t n, const int32_t *__restrict__ el2v, const double *__restrict__ lset,
+                                                      uint32_t *__restrict__ words, int64_t nwords, int8_t *__restrict__ dom_out,
+                                                      double *__restrict__ ratio, unsigned long long *__restrict__ err) {
+  const int64_t e = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  int dom = -2;
+  if (e < n) {
+    const double a = __ldg(lset + __ldg(el2v + 2 * e)), b = __ldg(lset + __ldg(el2v + 2 * e + 1));
+    const bool haspos = a > 0.0 || b > 0.0, hasneg = a < 0.0 || b < 0.0, haszero = a == 0.0 || b == 0.0;
+    if (haspos && hasneg) dom = haszero ? -1 : IF;
+    else if (!haspos && !hasneg) dom = -1;
+    else dom = hasneg ? NEG : POS;
+    if (dom == -1 && err) {
+      atomicAdd(&err[0], 1ULL);
+      atomicMin(reinterpret_cast<long long *>(&err[1]), (long long)e);
+    }
+    if (dom_out) dom_out[e] = (int8_t)dom;
+    if (ratio) {
+      const double t = a / (a - b);                   // fraction of the segment on vertex 0's side
+      ratio[e] = dom == NEG ? 1.0 : (dom == POS ? 0.0 : (dom == IF ? (a < 0.0 ? t : 1.0 - t) : nan("")));
+    }
+  }
+  const unsigned bn = __ballot_sync(0xffffffffu, dom == NEG), bp = __ballot_sync(0xffffffffu, dom == POS);
+  const unsigned bi = __ballot_sync(0xffffffffu, dom == IF), ba = __ballot_sync(0xffffffffu, dom != -2);
+  const int lane = threadIdx.x & 31;
+  const int64_t w = e >> 5;
+  if (words && lane < 8 && w < nwords) {
+    const unsigned sel = lane == NGSX_CDOM_ANY ? ba : (((lane & 1) ? bn : 0u) | ((lane & 2) ? bp : 0u) | ((lane & 4) ? bi : 0u));
+    words[lane * nwords + w] = sel;
+  }
+}
+
 __global__ void k_node_marks(int64_t ne, int npe, const int32_t *__restrict__ el2node, const int8_t *__restrict__ dom,
                              const double *__restrict__ ratio, int cell_mode, uint32_t *__restrict__ cut_nb, int32_t *__restrict__ dom_of_node) {
   int64_t e = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
@@ -717,14 +750,21 @@ __global__ void k_i32_to_i64(int64_t n, const int32_t *__restrict__ in, int64_t 
 }
 
 // facet marking (xfem/cutinfo.cpp:191-255), one thread per facet, ballot -> word
-__global__ void __launch_bounds__(256) k_facets_neighbor_types(int64_t nf, const int32_t *__restrict__ f2e, const uint32_t *__restrict__ a,
+__global__ void __launch_bounds__(256) k_facets_neighbor_types(int64_t nf, const int32_t *__restrict__ f2e, const int32_t *__restrict__ periodic,
+                                                              const uint32_t *__restrict__ a,
                                                               const uint32_t *__restrict__ b, int bva, int bvb, int use_and,
                                                               uint32_t *__restrict__ out) {
   int64_t f = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
   bool r = false;
   if (f < nf) {
     int e0 = f2e[2 * f], e1 = f2e[2 * f + 1];
-    if (e0 >= 0) {
+    bool skip = false;
+    if (periodic && e0 >= 0 && e1 < 0) {             // xfem/cutinfo.cpp:225-236: the partner's element, seen from the facet of the smaller number only
+      const int f2 = periodic[f];
+      if (f2 > f) e1 = f2e[2 * (int64_t)f2];
+      else if (f2 >= 0) skip = true;
+    }
+    if (e0 >= 0 && !skip) {
       bool al = (a[e0 >> 5] >> (e0 & 31)) & 1, bl = (b[e0 >> 5] >> (e0 & 31)) & 1;
       bool ar = e1 >= 0 ? ((a[e1 >> 5] >> (e1 & 31)) & 1) : (bva != 0);
       bool br = e1 >= 0 ? ((b[e1 >> 5] >> (e1 & 31)) & 1) : (bvb != 0);
@@ -828,6 +868,24 @@ int ngsx_classify(const ngsx_mesh *mesh, const double *lset_v, uint32_t *cdom_wo
   if (tmp) cudaFreeAsync(tmp, st);
   NGSX_CUDA(e0);
   NGSX_CUDA(e1);
+  return NGSX_OK;
+}
+
+int ngsx_classify_bnd(int dim, int64_t nbe, const int32_t *bnd_el2v, const double *lset_v, uint32_t *cdom_words, int8_t *dom,
+                      double *ratio, int64_t *err, void *stream) {
+  NGSX_REQUIRE(dim == 2 || dim == 3, "classify_bnd: mesh dimension must be 2 or 3");
+  NGSX_REQUIRE(nbe >= 0 && (nbe == 0 || (bnd_el2v && lset_v)), "classify_bnd: bad arguments");
+  cudaStream_t st = as_stream(stream);
+  if (dim == 3) {                                    // boundary triangles: the sign test and the part volumes need no coordinates
+    ngsx_mesh bm{};
+    bm.dim = 2; bm.ne = nbe; bm.nv = 0; bm.vert = lset_v; bm.el2v = bnd_el2v;
+    return ngsx_classify(&bm, lset_v, cdom_words, dom, ratio, err, stream);
+  }
+  if (err) { if (int rc = reset_err(err, st)) return rc; }
+  if (nbe == 0) return NGSX_OK;
+  k_classify_segm<<<nblocks(nbe, 256), 256, 0, st>>>(nbe, bnd_el2v, lset_v, cdom_words, (nbe + 31) / 32, dom, ratio,
+                                                      reinterpret_cast<unsigned long long *>(err));
+  NGSX_LAUNCH_CHECK();
   return NGSX_OK;
 }
 
@@ -959,7 +1017,16 @@ int ngsx_facets_neighbor_types(int64_t nf, const int32_t *facet2el, const uint32
                                int bnd_val_a, int bnd_val_b, int use_and, uint32_t *out_words, void *stream) {
   NGSX_REQUIRE(nf >= 0 && (nf == 0 || (facet2el && a_words && b_words && out_words)), "facets_neighbor_types: bad arguments");
   if (nf == 0) return NGSX_OK;
-  k_facets_neighbor_types<<<nblocks(nf, 256), 256, 0, as_stream(stream)>>>(nf, facet2el, a_words, b_words, bnd_val_a, bnd_val_b, use_and, out_words);
+  k_facets_neighbor_types<<<nblocks(nf, 256), 256, 0, as_stream(stream)>>>(nf, facet2el, nullptr, a_words, b_words, bnd_val_a, bnd_val_b, use_and, out_words);
+  NGSX_LAUNCH_CHECK();
+  return NGSX_OK;
+}
+
+int ngsx_facets_neighbor_types_periodic(int64_t nf, const int32_t *facet2el, const int32_t *periodic_facet, const uint32_t *a_words,
+                                        const uint32_t *b_words, int bnd_val_a, int bnd_val_b, int use_and, uint32_t *out_words, void *stream) {
+  NGSX_REQUIRE(nf >= 0 && (nf == 0 || (facet2el && periodic_facet && a_words && b_words && out_words)), "facets_neighbor_types_periodic: bad arguments");
+  if (nf == 0) return NGSX_OK;
+  k_facets_neighbor_types<<<nblocks(nf, 256), 256, 0, as_stream(stream)>>>(nf, facet2el, periodic_facet, a_words, b_words, bnd_val_a, bnd_val_b, use_and, out_words);
   NGSX_LAUNCH_CHECK();
   return NGSX_OK;
 }

@@ -106,6 +106,15 @@ class SimplexMesh:
             self._cache["facets"] = (el2f, f2e)
         return self._cache["facets"]
 
+    def boundary_elements(self):
+        """el2v [nbe][dim] int32 of the boundary elements (facets with one neighbour; NGSolve's surface / segment elements),
+        in facet order"""
+        if "bnd" not in self._cache:
+            _, f2e = self.facets()
+            f2v = self.edges()[0] if self.dim == 2 else self.faces()[0]
+            self._cache["bnd"] = f2v[f2e[:, 1] < 0].to(torch.int32).contiguous()
+        return self._cache["bnd"]
+
     # ---- H1 dof table ------------------------------------------------------------------------------
     def h1_dofs(self, order):
         """(el2dof [ne, ndof_el] i32, ndof) for H1 of the given order (1..3)."""

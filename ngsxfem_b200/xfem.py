@@ -91,6 +91,8 @@ class CutInfo:
             return self
         check(L.ngsx_classify(ctypes.byref(self.mesh.c_struct()), _ptr(lv), _ptr(self.words), _ptr(self.dom), _ptr(self.ratio),
                               _ptr(self.err), _stream()))
+        self._bnd = None                                             # the BND pass (xfem/cutinfo.cpp:47, 67) runs when it is asked for
+        self._bnd_lv = lv
         if node_marks:
             self._node_marks()
         return self
@@ -124,10 +126,26 @@ class CutInfo:
     def GetElementsOfType(self, domain_type=IF, VOL_or_BND=VOL) -> BitArray:
         """domain_type: DOMAIN_TYPE (NEG/POS/IF) or COMBINED_DOMAIN_TYPE (HASNEG, ...; the module constants are wrapped ints so
         the two reference enums, which share small integers, stay distinguishable) -- xfem/python_xfem.cpp:91-118."""
-        if VOL_or_BND != VOL:
-            raise NgsxError(-2, "boundary-element CutInfo is outside the CUDA path")
         cdt = domain_type.cdt if isinstance(domain_type, _CDT) else _DT2CDT[int(domain_type)]
+        if VOL_or_BND != VOL:
+            words, _, _ = self._boundary()
+            return BitArray(self.mesh.boundary_elements().shape[0], words[cdt])
         return BitArray(self.mesh.ne, self.words[cdt])
+
+    def _boundary(self):
+        """CutInformation::Update's BND pass (xfem/cutinfo.cpp:47, 67-120): the same classification on the boundary elements"""
+        if getattr(self, "_bnd", None) is None:
+            if getattr(self.mesh, "tensor", False):
+                raise NgsxError(-2, "boundary elements of quadrilateral / hexahedral meshes are outside the CUDA path")
+            bel = self.mesh.boundary_elements()
+            nbe, dev = bel.shape[0], self.mesh.device
+            words = torch.zeros((8, (nbe + 31) // 32), dtype=torch.int32, device=dev)
+            dom = torch.zeros(nbe, dtype=torch.int8, device=dev)
+            ratio = torch.zeros(nbe, dtype=torch.float64, device=dev)
+            err = torch.zeros(2, dtype=torch.int64, device=dev)
+            check(_lib_().ngsx_classify_bnd(self.mesh.dim, nbe, _ptr(bel), _ptr(self._bnd_lv), _ptr(words), _ptr(dom), _ptr(ratio), _ptr(err), _stream()))
+            self._bnd = (words, dom, ratio)
+        return self._bnd
 
     def GetFacetsOfType(self, domain_type=IF) -> BitArray:
         # Appendix C.1: facets_of_domain_type is never updated by the reference: NEG all ones, POS/IF all zeros
@@ -136,7 +154,7 @@ class CutInfo:
         return ba.Set() if int(domain_type) == NEG and not isinstance(domain_type, _CDT) else ba
 
     def GetCutRatios(self, VOL_or_BND=VOL) -> torch.Tensor:
-        return self.ratio
+        return self.ratio if VOL_or_BND == VOL else self._boundary()[2]
 
 
 class _CDT(int):
@@ -158,6 +176,11 @@ def GetFacetsWithNeighborTypes(mesh: Mesh, a: BitArray, bnd_val_a: bool = True, 
         b = a
     _, f2e = mesh.facets()
     out = BitArray(f2e.shape[0], device=mesh.device)
+    per = getattr(mesh, "periodic_facet", None)                      # MeshAccess::GetPeriodicFacet per facet (int32 [nf]) on periodic meshes
+    if per is not None:
+        check(_lib_().ngsx_facets_neighbor_types_periodic(f2e.shape[0], _ptr(f2e), _ptr(per), _ptr(a.words), _ptr(b.words), int(bnd_val_a),
+                                                          int(bnd_val_b), int(use_and), _ptr(out.words), _stream()))
+        return out
     check(_lib_().ngsx_facets_neighbor_types(f2e.shape[0], _ptr(f2e), _ptr(a.words), _ptr(b.words), int(bnd_val_a), int(bnd_val_b),
                                              int(use_and), _ptr(out.words), _stream()))
     return out
@@ -175,6 +198,26 @@ def GetDofsOfElements(space: H1, a: BitArray, heapsize: int = 1000000) -> BitArr
     """xfem/cutinfo.cpp:281-304"""
     out = BitArray(space.ndof, device=space.mesh.device)
     check(_lib_().ngsx_dofs_of_elements(space.mesh.ne, space.nd, _ptr(space.el2dof), _ptr(a.words), space.ndof, _ptr(out.words), _stream()))
+    return out
+
+
+def GetDofsOfFacets(space: H1, a: BitArray, heapsize: int = 1000000) -> BitArray:
+    """xfem/cutinfo.cpp:306-329: the dofs FESpace::GetDofNrs(NodeId(NT_FACET, f)) associates with the marked facets -- for an H1
+    space the INNER dofs of the facet (edge dofs in 2D, face dofs in 3D; NGS/comp/h1hofespace.cpp GetDofNrs(NodeId)), not the
+    vertex dofs.  Same kernel as GetDofsOfElements on the facet -> dof table."""
+    mesh = space.mesh
+    out = BitArray(space.ndof, device=mesh.device)
+    nf = mesh.nfacet
+    if mesh.dim == 2:
+        per, base = space.order - 1, mesh.nv                         # edge f: dofs nv + f (order - 1) + k
+    else:
+        per = 1 if space.order >= 3 else 0                           # face f: one dof at order 3, after the vertex and edge dofs
+        base = mesh.nv + mesh.edges()[0].shape[0] * (space.order - 1)
+    if per <= 0 or nf == 0:
+        return out
+    f = torch.arange(nf, device=mesh.device, dtype=torch.int64)
+    table = (base + f[:, None] * per + torch.arange(per, device=mesh.device)[None, :]).to(torch.int32).contiguous()
+    check(_lib_().ngsx_dofs_of_elements(nf, per, _ptr(table), _ptr(a.words), space.ndof, _ptr(out.words), _stream()))
     return out
 
 

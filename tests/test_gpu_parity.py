@@ -1603,3 +1603,84 @@ def test_plans_survive_a_moving_level_set(X):
     a1.Assemble(); f1.Assemble()
     assert torch.equal(a0.mat.rowptr, a1.mat.rowptr) and torch.equal(a0.mat.colidx, a1.mat.colidx)
     assert torch.equal(a0.mat.vals, a1.mat.vals) and torch.equal(f0.vec, f1.vec)
+
+
+@pytest.mark.parametrize("dim", [2, 3])
+def test_dofs_of_facets_bnd_classification_periodic_facets(X, dim):
+    """a-3 / a-2 remainder: GetDofsOfFacets (xfem/cutinfo.cpp:306-329), the BND pass of CutInformation::Update (:47, 67-120) and
+    the periodic-partner branch of GetFacetsWithNeighborTypes (:225-236), against numpy restatements"""
+    xf, ngs = X.xfem, X.ngs
+    m = X.meshes.MakeStructured2DMesh(8) if dim == 2 else X.meshes.MakeStructured3DMesh(5)
+    mesh = ngs.Mesh(m)
+    gf = ngs.GridFunction(ngs.H1(mesh, order=1))
+    xf.InterpolateToP1(ngs.SphereLevelset((0.1,) * dim, 0.47), gf)               # the interface meets the boundary
+    ci = xf.CutInfo(mesh, gf)
+    _, f2e = mesh.facets()
+    f2e_h = f2e.cpu().numpy()
+    nf = f2e_h.shape[0]
+    rng = np.random.default_rng(4)
+    fa = rng.uniform(size=nf) < 0.3
+    ba = ngs.BitArray.from_bool(dev(fa))
+    for order in (1, 2, 3):
+        V = ngs.H1(mesh, order=order)
+        got = xf.GetDofsOfFacets(V, ba).to_bool().cpu().numpy()
+        want = np.zeros(V.ndof, dtype=bool)
+        ned = mesh.edges()[0].shape[0]
+        if dim == 2 and order >= 2:                                                  # inner dofs of the marked edges
+            for k in range(order - 1):
+                want[mesh.nv + np.nonzero(fa)[0] * (order - 1) + k] = True
+        if dim == 3 and order >= 3:                                                  # the face dof
+            want[mesh.nv + ned * (order - 1) + np.nonzero(fa)[0]] = True
+        assert np.array_equal(got, want), order
+    # BND elements: facets with one neighbour, classified from their vertex values; cut ratio of a boundary element
+    bel = mesh.boundary_elements().cpu().numpy()
+    assert len(bel) == int((f2e_h[:, 1] < 0).sum()) and bel.shape[1] == dim
+    lv = gf.vec.cpu().numpy()[bel]
+    want_dom = np.where((lv > 0).any(1) & (lv < 0).any(1), IF, np.where((lv < 0).any(1), NEG, POS))
+    for dt, cdt in ((NEG, xf.CDOM_NEG), (POS, xf.CDOM_POS), (IF, xf.CDOM_IF)):
+        assert np.array_equal(ci.GetElementsOfType(cdt, ngs.BND).to_bool().cpu().numpy(), want_dom == dt)
+    assert np.array_equal(ci.GetElementsOfType(xf.HASNEG, ngs.BND).to_bool().cpu().numpy(), want_dom != POS)
+    assert (want_dom == IF).any()
+    r = ci.GetCutRatios(ngs.BND).cpu().numpy()
+    assert (r[want_dom == NEG] == 1).all() and (r[want_dom == POS] == 0).all()
+    from oracle import orc
+    for e in np.nonzero(want_dom == IF)[0][:50]:
+        if dim == 2:
+            a, b = lv[e]
+            t = a / (a - b)
+            assert abs(r[e] - (t if a < 0 else 1 - t)) <= 1e-14
+        else:                                                                        # triangle: NEG area fraction by the order-0 rules
+            pm = np.array([[1.0, 0.0], [0.0, 1.0], [0.0, 0.0]])
+            _, rr = orc.cutinfo_element(2, pm, lv[e])
+            assert abs(r[e] - rr) <= 1e-14
+    # periodic identification of the x = 0 and x = 1 boundary facets
+    fc = (mesh.edges()[0] if dim == 2 else mesh.faces()[0]).cpu().numpy()
+    cen = mesh.vert.cpu().numpy()[fc].mean(axis=1)
+    left = np.nonzero((f2e_h[:, 1] < 0) & (np.abs(cen[:, 0]) < 1e-12))[0]
+    right = np.nonzero((f2e_h[:, 1] < 0) & (np.abs(cen[:, 0] - 1) < 1e-12))[0]
+    key = lambda idx: np.lexsort(cen[idx][:, 1:].T[::-1])
+    left, right = left[key(left)], right[key(right)]
+    assert len(left) == len(right) > 0 and np.allclose(cen[left][:, 1:], cen[right][:, 1:])
+    per = np.full(nf, -1, dtype=np.int32)
+    per[left], per[right] = right, left
+    A = rng.uniform(size=mesh.ne) < 0.5
+    B = rng.uniform(size=mesh.ne) < 0.5
+    bA, bB = ngs.BitArray.from_bool(dev(A)), ngs.BitArray.from_bool(dev(B))
+    for use_and in (True, False):
+        mesh.periodic_facet = dev(per)
+        got = xf.GetFacetsWithNeighborTypes(mesh, bA, False, True, use_and, bB).to_bool().cpu().numpy()
+        mesh.periodic_facet = None
+        want = np.zeros(nf, dtype=bool)
+        for f in range(nf):
+            e0, e1 = f2e_h[f]
+            if e1 < 0:
+                if per[f] > f:
+                    e1 = f2e_h[per[f], 0]
+                elif per[f] >= 0:
+                    continue
+            al, bl = A[e0], B[e0]
+            ar, br = (A[e1], B[e1]) if e1 >= 0 else (False, True)
+            want[f] = ((al and br) or (ar and bl)) if use_and else (al or br or ar or bl)
+        assert np.array_equal(got, want)
+        plain = xf.GetFacetsWithNeighborTypes(mesh, bA, False, True, use_and, bB).to_bool().cpu().numpy()
+        assert not np.array_equal(plain, got) or not use_and
