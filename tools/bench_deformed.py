@@ -39,6 +39,9 @@ def main():
     u, v = Vh.TnT()
     form = ngs.grad(u) * ngs.grad(v) + u * v
     ev = lambda: torch.cuda.Event(enable_timing=True)
+    import bench
+    clocks = bench.ClockSampler(0)
+    clocks.start()
 
     def timed(fn):
         for _ in range(3):
@@ -74,11 +77,21 @@ def main():
             import ctypes
             mc = ctypes.byref(mesh.c_struct())
             st = ctypes.c_void_p(torch.cuda.current_stream().cuda_stream)
-            t_el, _ = timed(lambda: L.ngsx_elmat_h1_deformed(mc, ctypes.byref(dd), lv.data_ptr(), 2, 0, 4, ctypes.byref(a.integrators[0].form), n,
-                                                             plan.els.data_ptr(), plan.mats.data_ptr(), None, None, st))
-            t_ga, _ = timed(lambda: L.ngsx_assemble_csr_rows_mats(plan.handle, plan.mats.data_ptr(), 0, a.mat.vals.data_ptr(), st))
-            out["ms"]["k_elmat_def"] = t_el
-            out["ms"]["k_rows_mats"] = t_ga
+            def elmat_packed():
+                L.ngsx_set_packed_output(plan.slots)
+                return L.ngsx_elmat_h1_deformed(mc, ctypes.byref(dd), lv.data_ptr(), 2, 0, 4, ctypes.byref(a.integrators[0].form), n,
+                                                plan.els.data_ptr(), plan.rows.data_ptr(), None, None, st)
+            t_el, _ = timed(elmat_packed)
+            t_ga, _ = timed(lambda: L.ngsx_assemble_csr_rows_packed(plan.handle, plan.rows.data_ptr(), 0, a.mat.vals.data_ptr(), st))
+            out["ms"]["k_elmat_def (packed rows)"] = t_el
+            out["ms"]["k_rows_packed"] = t_ga
+            dense = torch.empty((n, 100), dtype=torch.float64, device=mesh.device)
+            t_eld, _ = timed(lambda: L.ngsx_elmat_h1_deformed(mc, ctypes.byref(dd), lv.data_ptr(), 2, 0, 4, ctypes.byref(a.integrators[0].form), n,
+                                                              plan.els.data_ptr(), dense.data_ptr(), None, None, st))
+            t_gad, _ = timed(lambda: L.ngsx_assemble_csr_rows_mats(plan.handle, dense.data_ptr(), 0, a.mat.vals.data_ptr(), st))
+            out["ms"]["k_elmat_def (dense blocks)"] = t_eld
+            out["ms"]["k_rows_mats (dense blocks)"] = t_gad
+            out["pairs"] = int(plan.npairs)
             out["elements_per_s_deformed_assemble"] = n / (t_asm * 1e-3)
             # algorithmic bytes of the deformed element-matrix kernel: 16 B el2v + 40 B deformation dofs + 10 x 24 B coefficients + 96 B
             # vertices + 32 B level set in, 800 B block out
@@ -99,12 +112,13 @@ def main():
         t0 = time.perf_counter()
         ref, _ = orc.elmat_mesh_iso(3, el2v, vert, ls, dord, e2dd, dv, 2, 0, 4, orc.form8(1.0, 1.0), els=sample)
         dt_s = time.perf_counter() - t0
-        got = a._plans[0].mats.reshape(-1, 10, 10)[::max(1, len(els) // 200000)].cpu().numpy()
+        got = dense.reshape(-1, 10, 10)[::max(1, len(els) // 200000)].cpu().numpy()
         out["sample_parity_rel"] = float((np.abs(got - ref).reshape(len(ref), -1).max(1) / np.abs(ref).reshape(len(ref), -1).max(1)).max())
         out["cpu_baseline"] = {"value": len(sample) / dt_s, "unit": "elements/s", "cores": orc.load().orc_max_threads(), "kind": "port",
                                "sample": f"{len(sample)} of the {len(els)} listed elements, element matrices only (orc_elmat_mesh_iso, OpenMP)"}
     except Exception as exc:
         out["cpu_baseline"] = {"error": f"{type(exc).__name__}: {str(exc)[:200]}"}
+    out["clocks"] = clocks.stop()
     print(json.dumps(out))
 
 
