@@ -362,6 +362,13 @@ int ngsx_facetpatch_table_h1(int64_t npatch, const int32_t *patch_els, int32_t n
 int ngsx_facetpatch_cmat_h1(const ngsx_mesh *mesh, int fe_order, double coef, int hpow, int64_t npatch,
                             const int32_t *patch_els, const uint8_t *cidx, int32_t ndp, double *mats, void *stream);
 
+/* the same on a deformed mesh (row f-4): a rule point of one element is pulled into the other through both isoparametric maps by
+ * the Newton iteration of MapPatchIntegrationPoint (xfem/symboliccutbfi.cpp:1113-1199: affine start, <= 200 steps, tolerance
+ * 1e-12 sqrt(det F), "low order guess" exit); weights mir1.GetWeight(), h = mesh_size on mir1 per point (:1359-1365) */
+int ngsx_facetpatch_cmat_h1_deformed(const ngsx_mesh *mesh, const ngsx_deformation *defo, int fe_order, double coef, int hpow,
+                                     int64_t npatch, const int32_t *patch_els, const uint8_t *cidx, int32_t ndp, double *mats,
+                                     void *stream);
+
 #ifdef __cplusplus
 }
 #endif

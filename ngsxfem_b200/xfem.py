@@ -461,8 +461,9 @@ class SymbolicFacetPatchBFI:
         if skeleton:
             raise NgsxError(-2, "skeleton=True (derivative-jump ghost penalty, xfem/ghostpenalty.cpp) is outside the CUDA path; "
                                 "use skeleton=False (facet-patch)")
-        if time_order >= 0 or deformation is not None:
-            raise NgsxError(-2, "space-time / deformed facet patches are outside the CUDA path")
+        if time_order >= 0:
+            raise NgsxError(-2, "space-time facet patches are outside the CUDA path")
+        self.deformation = deformation                     # None: the mesh's (MapPatchIntegrationPoint through both curved maps)
         terms = form.collect()
         want = {("u", "v"): 1.0, ("uo", "v"): -1.0, ("u", "vo"): -1.0, ("uo", "vo"): 1.0}
         if set(terms) != set(want):
@@ -766,9 +767,11 @@ class BilinearForm:
             self._graph_key = xver
         if fes.mesh.deformation is not None or any(getattr(i, "deformation", None) is not None for i in self.integrators):
             for integ in self.integrators:                         # what the deformed path covers
-                if not isinstance(integ, SymbolicCutBFI) or integ.xterms is not None or self.assembly != "rows":
-                    raise NgsxError(-2, "on a deformed mesh only SymbolicCutBFI integrators on H1 through the row gather are on the "
-                                        "CUDA path (facet patches, XFESpace and the coloured scatter: undeformed only); no CPU fallback")
+                if isinstance(integ, SymbolicFacetPatchBFI):
+                    continue
+                if integ.xterms is not None or self.assembly != "rows":
+                    raise NgsxError(-2, "on a deformed mesh SymbolicCutBFI integrators on H1 through the row gather and facet patches are on "
+                                        "the CUDA path (XFESpace and the coloured scatter: undeformed only); no CPU fallback")
         plans = [self._plan_for(k, integ) for k, integ in enumerate(self.integrators)]
         # a single row plan that covers every stored entry overwrites its rows: no SetZero pass, each value written once
         # (with a row range: the rank's rows are one contiguous CSR span, the other rows belong to other ranks and stay untouched)
@@ -900,8 +903,14 @@ class BilinearForm:
             return
         slots, rows = _packed_rows(plan, plan.ndp)                     # the kernel writes block rows where the gather's schedule reads them
         L.ngsx_set_packed_output(slots)
-        check(L.ngsx_facetpatch_cmat_h1(ctypes.byref(fes.mesh.c_struct()), fes.order, integ.coef, integ.hpow, npatch,
-                                        _ptr(plan.els), _ptr(plan.cidx), plan.ndp, _ptr(rows), _stream()))
+        gfd = self._deformation_of(integ)
+        if gfd is not None:                                            # deformed mesh: Newton pull-back through both curved maps
+            defo = fes.mesh.c_deformation(gfd)
+            check(L.ngsx_facetpatch_cmat_h1_deformed(ctypes.byref(fes.mesh.c_struct()), ctypes.byref(defo), fes.order, integ.coef, integ.hpow,
+                                                     npatch, _ptr(plan.els), _ptr(plan.cidx), plan.ndp, _ptr(rows), _stream()))
+        else:
+            check(L.ngsx_facetpatch_cmat_h1(ctypes.byref(fes.mesh.c_struct()), fes.order, integ.coef, integ.hpow, npatch,
+                                            _ptr(plan.els), _ptr(plan.cidx), plan.ndp, _ptr(rows), _stream()))
         check(L.ngsx_assemble_csr_rows_packed(plan.handle, _ptr(rows), 1, _ptr(self.mat.vals), _stream()))
 
     def elmats(self, k: int = 0):

@@ -1164,6 +1164,86 @@ int orc_facetpatch_elmat_h1(int dim, int fe_order, const int *vn1, const double 
   return 2*nr;
 }
 
+/* MapPatchIntegrationPoint (xfem/symboliccutbfi.cpp:1113-1199) through isoparametric maps: the point xi_from of the `from`
+ * element is pulled into the `to` element by Newton's method (start: the affine map through the reference vertices, :1141-1166;
+ * at most 200 steps; the loop stops when the residual BEFORE the last update was <= 1e-12 sqrt(det F_from), :1168-1180 -- with a
+ * negative Jacobian determinant the bound is NaN and exactly one step is taken).  Returns the weight the reference stores:
+ * from_weight / measure_to, measure_to = |det F_to| at the point of the last evaluation (:1179, 1193). */
+static double map_patch_point(int dim, int dord, const double *g_from, const double *g_to, const double *xi_from, double w_ref,
+                              double *xi_to)
+{
+  double x[3], J[3][3], Ji[3][3], det;
+  iso_eval(dim, dord, g_from, xi_from, x, J, Ji, &det);
+  const double h = sqrt(det);
+  const double wfrom = fabs(det) * w_ref;                       /* mip.GetWeight() */
+  double z[3] = {0, 0, 0}, x0[3], A[3][3], Ai[3][3], f[3], pm[12], t[3][3], d0;
+  iso_eval(dim, dord, g_to, z, x0, t, Ai, &d0);
+  for (int d = 0; d < dim; d++) {
+    double e[3] = {0, 0, 0}, xe[3];
+    e[d] = 1.0;
+    iso_eval(dim, dord, g_to, e, xe, t, Ai, &d0);
+    for (int r = 0; r < dim; r++) A[r][d] = xe[r] - x0[r];
+  }
+  for (int k = 0; k < dim; k++) for (int r = 0; r < dim; r++) pm[k*dim + r] = A[r][k];
+  for (int r = 0; r < dim; r++) pm[dim*dim + r] = 0.0;
+  affine_t AA;
+  affine_init(dim, pm, &AA);
+  const double w00 = fabs(AA.det);
+  double xi00[3] = {0, 0, 0}, xi[3] = {0, 0, 0};
+  for (int r = 0; r < dim; r++) f[r] = x[r] - x0[r];
+  for (int k = 0; k < dim; k++) { double v = 0; for (int r = 0; r < dim; r++) v += AA.Jinv[k][r] * f[r]; xi00[k] = v; xi[k] = v; }
+  int its = 0;
+  double w = 0, nrm = 0;
+  while (its == 0 || (nrm > 1e-12 * h && its < 200)) {
+    double xq[3], Jq[3][3], Jqi[3][3], dq, diff[3];
+    iso_eval(dim, dord, g_to, xi, xq, Jq, Jqi, &dq);
+    nrm = 0;
+    for (int r = 0; r < dim; r++) { diff[r] = x[r] - xq[r]; nrm += diff[r]*diff[r]; }
+    nrm = sqrt(nrm);
+    for (int k = 0; k < dim; k++) { double v = 0; for (int r = 0; r < dim; r++) v += Jqi[k][r] * diff[r]; xi[k] += v; }
+    its++;
+    w = fabs(dq);
+  }
+  if (its >= 200) { for (int k = 0; k < 3; k++) xi_to[k] = xi00[k]; return wfrom / w00; }
+  for (int k = 0; k < 3; k++) xi_to[k] = xi[k];
+  return wfrom / w;
+}
+
+/* SymbolicFacetPatchBilinearFormIntegrator::CalcFacetMatrix (:1202-1411) on a DEFORMED mesh (isoparametric elements of order
+ * dord, geometry coefficients g1 / g2), form coef h^hpow (u - u.Other())(v - v.Other()); h = specialcf.mesh_size on mir1 per point.
+ * Pinned against ref_facetpatch_elmat_h1 (the reference's own MapPatchIntegrationPoint). */
+int orc_facetpatch_elmat_h1_iso(int dim, int fe_order, int dord, const int *vn1, const double *g1, const int *vn2, const double *g2,
+                                double coef, int hpow, double *elmat)
+{
+  int nd = orc_h1_ndof(dim, fe_order), n2 = 2*nd;
+  const double (*r)[4];
+  int nr = select_rule(dim, 2*fe_order, &r);
+  if (nr < 0) return nr;
+  for (int i = 0; i < n2*n2; i++) elmat[i] = 0;
+  double sh1[ORC_MAXND], sh2[ORC_MAXND], dref[ORC_MAXND*3], jump[2*ORC_MAXND];
+  for (int l = 0; l < 2*nr; l++) {
+    double xi1[3] = {0, 0, 0}, xi2[3] = {0, 0, 0}, w1;
+    if (l < nr) {
+      for (int k = 0; k < 3; k++) xi1[k] = r[l][k];
+      map_patch_point(dim, dord, g1, g2, xi1, r[l][3], xi2);
+      w1 = r[l][3];
+    } else {
+      for (int k = 0; k < 3; k++) xi2[k] = r[l - nr][k];
+      w1 = map_patch_point(dim, dord, g2, g1, xi2, r[l - nr][3], xi1);
+    }
+    double x[3], J[3][3], Ji[3][3], det;
+    iso_eval(dim, dord, g1, xi1, x, J, Ji, &det);                 /* mir1[l] */
+    double hh = pow(fabs(det), 1.0 / dim);
+    double val = coef * pow(hh, hpow) * (fabs(det) * w1);
+    orc_h1_shape(dim, fe_order, vn1, xi1, sh1, dref);
+    orc_h1_shape(dim, fe_order, vn2, xi2, sh2, dref);
+    for (int i = 0; i < nd; i++) { jump[i] = sh1[i]; jump[nd + i] = -sh2[i]; }
+    for (int i = 0; i < n2; i++)
+      for (int j = 0; j < n2; j++) elmat[i*n2 + j] += val * jump[i] * jump[j];
+  }
+  return 2*nr;
+}
+
 int orc_max_threads(void)
 {
 #ifdef _OPENMP

@@ -76,6 +76,7 @@ def load():
     L.orc_elmat_mesh_iso.restype = c_i64
     L.orc_quad_rule_untrafo.argtypes = [dp, c_int, c_int, dp, dp, c_int]
     L.orc_set_threads.argtypes = [c_int]
+    L.orc_facetpatch_elmat_h1_iso.argtypes = [c_int, c_int, c_int, ip, dp, ip, dp, c_double, c_int, dp]
     L.orc_csr_pattern.argtypes = [c_i64, c_int, ip, c_i64, lp, ip]
     L.orc_csr_pattern.restype = c_i64
     L.orc_color_elements.argtypes = [c_i64, c_int, ip, c_i64, lp, lp]

@@ -1684,3 +1684,74 @@ def test_dofs_of_facets_bnd_classification_periodic_facets(X, dim):
         assert np.array_equal(got, want)
         plain = xf.GetFacetsWithNeighborTypes(mesh, bA, False, True, use_and, bB).to_bool().cpu().numpy()
         assert not np.array_equal(plain, got) or not use_and
+
+
+@pytest.mark.parametrize("dim", [2, 3])
+@pytest.mark.parametrize("fo,dord", [(1, 1), (1, 2), (2, 2)])
+def test_deformed_facet_patches_against_oracle(X, dim, fo, dord):
+    """row f-4: ghost-penalty facet patches on a DEFORMED mesh (Newton pull-back of MapPatchIntegrationPoint) -- the fictitious-
+    domain operator of py_tutorials/fictdom_ghostpen.py:86-107 (NEG stiffness + 0.1/h^2 patch penalty) after mesh.SetDeformation,
+    merged blocks and the assembled operator against the oracle (pinned vs the compiled reference, tests/test_oracle_vs_ref.py)"""
+    from oracle import orc
+    import scipy.sparse as sp
+    mesh, gf, defo, Vd = _deformed_setup(X, dim, dord, amp=0.04)
+    xf, ngs = X.xfem, X.ngs
+    mesh.SetDeformation(defo)
+    ci = xf.CutInfo(mesh, gf)
+    hasneg, hasif = ci.GetElementsOfType(xf.HASNEG), ci.GetElementsOfType(IF)
+    ba = xf.GetFacetsWithNeighborTypes(mesh, a=hasneg, b=hasif)
+    Vh = ngs.H1(mesh, order=fo, dgjumps=True)
+    u, v = Vh.TnT()
+    h = ngs.specialcf.mesh_size
+    a = xf.RestrictedBilinearForm(Vh, element_restriction=hasneg, facet_restriction=ba)
+    a += xf.SymbolicBFI(levelset_domain={"levelset": gf, "domain_type": NEG}, form=ngs.grad(u) * ngs.grad(v), definedonelements=hasneg)
+    a += xf.SymbolicFacetPatchBFI(form=0.1 * 1.0 / h * 1.0 / h * (u - u.Other()) * (v - v.Other()), skeleton=False, definedonelements=ba)
+    a.Assemble()
+    first = a.mat.vals.clone()
+    a.mat.vals.fill_(float("nan"))
+    a.Assemble()
+    assert torch.equal(first, a.mat.vals)                                       # bitwise reproducible
+    plan = a._plans[1]
+    ndp, npatch = plan.ndp, plan.els.shape[0]
+    assert npatch > 10
+    dd = mesh.c_deformation()
+    dmats = torch.empty((npatch, ndp * ndp), dtype=torch.float64, device="cuda")
+    X.lib.check(X.lib.load().ngsx_facetpatch_cmat_h1_deformed(ctypes.byref(mesh.c_struct()), ctypes.byref(dd), fo, 0.1, -2, npatch,
+                                                              plan.els.data_ptr(), plan.cidx.data_ptr(), ndp, dmats.data_ptr(),
+                                                              torch.cuda.current_stream().cuda_stream))
+    el2v, vert, e2d, ls = mesh.el2v.cpu().numpy(), mesh.vert.cpu().numpy(), Vh.el2dof.cpu().numpy(), gf.vec.cpu().numpy()
+    e2dd, dv = Vd.el2dof.cpu().numpy(), defo.vec.cpu().numpy()
+
+    def gcoef(e):
+        g = dv[e2dd[e]].copy()
+        g[: dim + 1] += vert[el2v[e]]
+        return g
+    pe, tab, mats = plan.els.cpu().numpy(), plan.table.cpu().numpy(), dmats.cpu().numpy()
+    A = sp.lil_matrix((Vh.ndof, Vh.ndof))
+    for k, (e0, e1) in enumerate(pe):
+        _, em = orc.facetpatch_elmat_h1(dim, fo, el2v[e0], gcoef(e0), el2v[e1], gcoef(e1), 0.1, -2, dord=dord)
+        d = np.concatenate([e2d[e0], e2d[e1]])
+        C = (tab[k][:, None] == d[None, :]).astype(float)
+        ref = C @ em @ C.T
+        assert np.abs(mats[k].reshape(ndp, ndp) - ref).max() <= 1e-11 * np.abs(em).max(), k
+        for i in range(len(d)):
+            for j in range(len(d)):
+                A[d[i], d[j]] += em[i, j]
+    els = np.nonzero(hasneg.to_bool().cpu().numpy())[0]
+    vol, _ = orc.elmat_mesh_iso(dim, el2v, vert, ls, dord, e2dd, dv, fo, NEG, 2 * fo - 2, orc.form8(0.0, 1.0), els=els)
+    nd = e2d.shape[1]
+    rows = np.repeat(e2d[els], nd, axis=1).reshape(-1); cols = np.tile(e2d[els], (1, nd)).reshape(-1)
+    ref = sp.csr_matrix((vol.reshape(-1), (rows, cols)), shape=(Vh.ndof, Vh.ndof)) + A.tocsr()
+    diff = abs(a.mat.to_scipy() - ref).max()
+    assert diff <= 1e-11 * abs(ref).max()
+    # a zero deformation reproduces the affine patch operator
+    zero = ngs.GridFunction(Vd)
+    mesh.SetDeformation(zero)
+    b = xf.RestrictedBilinearForm(Vh, element_restriction=hasneg, facet_restriction=ba)
+    b += xf.SymbolicFacetPatchBFI(form=0.1 * 1.0 / h * 1.0 / h * (u - u.Other()) * (v - v.Other()), skeleton=False, definedonelements=ba)
+    b.Assemble()
+    mesh.UnsetDeformation()
+    c = xf.RestrictedBilinearForm(Vh, element_restriction=hasneg, facet_restriction=ba)
+    c += xf.SymbolicFacetPatchBFI(form=0.1 * 1.0 / h * 1.0 / h * (u - u.Other()) * (v - v.Other()), skeleton=False, definedonelements=ba)
+    c.Assemble()
+    assert (b.mat.vals - c.mat.vals).abs().max().item() <= 1e-11 * c.mat.vals.abs().max().item()
