@@ -352,6 +352,12 @@ int ngsx_xfem_elmat_h1(const ngsx_mesh *mesh, const double *lset_v, int fe_order
                        const ngsx_xterm *h_terms, int64_t nlist, const int32_t *els, const int8_t *xsign, const double *ratio,
                        int accumulate, double *mats, void *stream);
 
+/* the same on a deformed mesh (row f-4; DiffOpX evaluates CalcMappedDShape on the deformed ElementTransformation,
+ * xfem/xfemdiffops.cpp:8-82): geometry, normal, interface weight factor and mesh_size per rule point */
+int ngsx_xfem_elmat_h1_deformed(const ngsx_mesh *mesh, const ngsx_deformation *defo, const double *lset_v, int fe_order, int dt,
+                                int intorder, int32_t nterms, const ngsx_xterm *h_terms, int64_t nlist, const int32_t *els,
+                                const int8_t *xsign, const double *ratio, int accumulate, double *mats, void *stream);
+
 /* Merged patch blocks for the row gather (NGSolve's compressed_dnums / compressed_elmat, NGS/comp/bilinearform.cpp:1800-1853).
  * ngsx_facetpatch_table_h1 (symbolic, synchronises): table [np][ndp] = dofs of element 0, then the dofs of element 1 that
  * element 0 does not have; cidx [np][2 nd] = position of every local dof of [dofs(el0) | dofs(el1)] in that list.

@@ -12,6 +12,7 @@
 // their blocks in one buffer (accumulate) and share one gather.
 #include <algorithm>
 #include "ngsx_host.cuh"
+#include "ngsx_iso.cuh"
 
 namespace ngsx {
 
@@ -356,26 +357,188 @@ static int launch_xfem(const ngsx_mesh &M, const double *lset, const DeviceData 
   return NGSX_OK;
 }
 
+// ---------------------------------------------------------------------------------------------------------------
+// DEFORMED mesh (row f-4): the same compound block with per-point geometry.  The monomial-moment formulation needs a constant
+// Jacobian, so here a WARP takes an element: lane q evaluates rule point q of a round of XDQ (isoparametric map, shapes, mapped
+// gradients, normal derivative, weight |det F| w [|F^-T n_ref|], the form's terms folded into 45 coefficients with the
+// point's mesh_size) into the warp's shared-memory stage, then every lane accumulates its entries of the (2 nd)^2 block.
+// Reference: DiffOpX on a deformed ElementTransformation (xfem/xfemdiffops.cpp:8-82 uses CalcMappedDShape(mip)).
+// ---------------------------------------------------------------------------------------------------------------
+constexpr int XDW = 4;            // warps per CTA
+constexpr int XDQ = 16;           // rule points staged per round
+
+struct XDefo { const int32_t *el2dof; const double *coef; };
+
+template <int DIM, int ORDER, int DORD>
+__global__ void __launch_bounds__(XDW * 32) k_xfem_def(ngsx_mesh M, XDefo D, const double *__restrict__ lset, const CutTable *__restrict__ tab, int dt,
+                                                      const double4 *__restrict__ rule_vol, int nr_vol, const double4 *__restrict__ rule_if,
+                                                      int nr_if, XTermsDev X, int64_t nlist, const int32_t *__restrict__ els,
+                                                      const int8_t *__restrict__ xsign, const double *__restrict__ ratio, int accumulate,
+                                                      double *__restrict__ mats, const int32_t *__restrict__ rowslot) {
+  constexpr int ND = H1<DIM, ORDER>::ND, N2C = 2 * ND, NE = N2C * N2C, NDG = H1<DIM, DORD>::ND, T = (NE + 31) / 32;
+  constexpr size_t PER_WARP = (size_t)XDQ * ND * 32 + ((size_t)XDQ * ND + XDQ + XDQ * XCO + NDG * DIM) * 8;
+  extern __shared__ __align__(16) unsigned char smem_raw[];
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  unsigned char *wbase = smem_raw + warp * PER_WARP;
+  double4 *stage = reinterpret_cast<double4 *>(wbase);
+  double *dnq = reinterpret_cast<double *>(wbase + (size_t)XDQ * ND * 32);
+  double *facq = dnq + XDQ * ND;
+  double *cq = facq + XDQ;
+  double *gc = cq + XDQ * XCO;
+  const bool IFACE = dt == IF;
+  const int64_t nwarps = (int64_t)gridDim.x * XDW;
+  for (int64_t k = (int64_t)blockIdx.x * XDW + warp; k < nlist; k += nwarps) {
+    const int64_t e = els ? els[k] : k;
+    const int32_t *ev = M.el2v + e * (DIM + 1);
+    double ls[4] = {0.0, 0.0, 0.0, 0.0};
+#pragma unroll
+    for (int a = 0; a <= DIM; a++) ls[a] = __ldg(lset + __ldg(ev + a));
+    __syncwarp();
+    for (int t = lane; t < NDG * DIM; t += 32) {
+      const int i = t / DIM, d = t % DIM;
+      double c = __ldg(D.coef + (int64_t)__ldg(D.el2dof + e * NDG + i) * DIM + d);
+      if (i <= DIM) c += __ldg(M.vert + (int64_t)__ldg(ev + i) * DIM + d);
+      gc[t] = c;
+    }
+    __syncwarp();
+    int mask;
+    const int dom = sign_test<DIM>(ls, mask);
+    const bool cut = dom == IF;
+    // this lane's entries (I, J) of the compound block and their block classes
+    const int8_t *sg = xsign + k * ND;
+    int ei[T], ej[T], ec[T];
+#pragma unroll
+    for (int t = 0; t < T; t++) {
+      const int idx = lane + 32 * t;
+      const int I = idx < NE ? idx / N2C : 0, J = idx < NE ? idx % N2C : 0;
+      const int bI = I >= ND, bJ = J >= ND;
+      ei[t] = I - bI * ND; ej[t] = J - bJ * ND;
+      ec[t] = (bI ? 1 + (int)__ldg(sg + ei[t]) : 0) * 3 + (bJ ? 1 + (int)__ldg(sg + ej[t]) : 0);
+    }
+    double acc[T];
+#pragma unroll
+    for (int t = 0; t < T; t++) acc[t] = 0.0;
+    if (cut || dom == dt) {
+      const double kap = __ldg(ratio + e);
+      double r2 = 0.0;
+#pragma unroll
+      for (int a = 0; a < DIM; a++) { const double v = ls[a] - ls[DIM]; r2 += v * v; }
+      const bool iface = cut && IFACE;
+      CutEntry E;
+      if (cut) E = tab->e[DIM - 2][dt][mask]; else { E.ns = 1; E.npt = 0; }
+      const double4 *rule = iface ? rule_if : rule_vol;
+      const int nr = iface ? nr_if : nr_vol;
+      for (int sidx = 0; sidx < E.ns; sidx++) {
+        double P[4][3];
+        double sfac = 1.0;
+        if (cut) {
+          for (int v = 0; v < E.npt; v++) coded_point<DIM>(E.v[sidx][v], ls, P[v]);
+          sfac = simplex_factor(E.npt, P);
+        }
+        for (int q0 = 0; q0 < nr; q0 += XDQ) {
+          const int nq = min(XDQ, nr - q0);
+          if (lane < nq) {
+            const double4 r = rule[q0 + lane];
+            double xi[3] = {r.x, r.y, r.z};
+            if (cut) simplex_point(E.npt, P, r, xi);
+            double lam[4] = {xi[0], xi[1], xi[2], 0.0}, last = 1.0;
+#pragma unroll
+            for (int a = 0; a < DIM; a++) last -= lam[a];
+            lam[DIM] = last;
+            double x[DIM], gl[DIM + 1][DIM], det;
+            iso_point<DIM, DORD>(GcWarp{gc}, lam, x, gl, det);
+            const double adet = fabs(det);
+            double nrm[DIM], g2 = 0.0;
+#pragma unroll
+            for (int d = 0; d < DIM; d++) {
+              double v = 0.0;
+#pragma unroll
+              for (int a = 0; a <= DIM; a++) v += ls[a] * gl[a][d];
+              nrm[d] = v; g2 += v * v;
+            }
+            const double gn = sqrt(g2), inv = 1.0 / gn;
+#pragma unroll
+            for (int d = 0; d < DIM; d++) nrm[d] *= inv;
+#pragma unroll
+            for (int i = 0; i < ND; i++) {
+              double sv, gv[DIM];
+              h1_shape_grad<DIM, ORDER>(i, lam, gl, sv, gv);
+              stage[lane * ND + i] = make_double4(sv, gv[0], gv[1], DIM == 3 ? gv[DIM - 1] : 0.0);
+              double dn = 0.0;
+#pragma unroll
+              for (int d = 0; d < DIM; d++) dn += gv[d] * nrm[d];
+              dnq[lane * ND + i] = dn;
+            }
+            facq[lane] = adet * (r.w * sfac * (iface ? gn / sqrt(r2) : 1.0));
+            const double h = DIM == 2 ? sqrt(adet) : cbrt(adet);        // specialcf.mesh_size at this point
+            for (int c = 0; c < 9; c++) {
+              double a5[5] = {0.0, 0.0, 0.0, 0.0, 0.0};
+              for (int t = X.cls[c]; t < X.cls[c + 1]; t++) {
+                const double kf = X.kappa[t] == 0 ? 1.0 : (X.kappa[t] == 1 ? kap : 1.0 - kap);
+                const double v = X.coef[t] * xipow(h, X.hpow[t]) * kf;
+                const int pr = X.pair[t];
+#pragma unroll
+                for (int qq = 0; qq < 5; qq++) a5[qq] += pr == qq ? v : 0.0;
+              }
+#pragma unroll
+              for (int qq = 0; qq < 5; qq++) cq[lane * XCO + c * 5 + qq] = a5[qq];
+            }
+          }
+          __syncwarp();
+          for (int q = 0; q < nq; q++) {
+            const double f = facq[q];
+#pragma unroll
+            for (int t = 0; t < T; t++) {
+              const double4 bi = stage[q * ND + ei[t]], bj = stage[q * ND + ej[t]];
+              const double di = dnq[q * ND + ei[t]], dj = dnq[q * ND + ej[t]];
+              const double *cf = cq + q * XCO + ec[t] * 5;
+              const double gg = bi.y * bj.y + bi.z * bj.z + (DIM == 3 ? bi.w * bj.w : 0.0);
+              // operator pairs (test, trial): 0 val-val, 1 val-dn, 2 dn-val, 3 dn-dn, 4 grad.grad
+              double v = cf[0] * (bi.x * bj.x);
+              v = fma(cf[1], bi.x * dj, v); v = fma(cf[2], di * bj.x, v); v = fma(cf[3], di * dj, v); v = fma(cf[4], gg, v);
+              acc[t] += f * v;
+            }
+          }
+          __syncwarp();
+        }
+      }
+    }
+#pragma unroll
+    for (int t = 0; t < T; t++) {
+      const int idx = lane + 32 * t;
+      if (idx < NE) {
+        const int I = idx / N2C, J = idx % N2C;
+        double *o = mats + k * NE + idx;
+        if (rowslot) {
+          const int sl = __ldg(rowslot + k * N2C + I);
+          o = sl >= 0 ? mats + (int64_t)sl * N2C + J : nullptr;
+        }
+        if (o) *o = accumulate ? *o + acc[t] : acc[t];
+      }
+    }
+  }
+}
+
+template <int DIM, int ORDER, int DORD>
+static int launch_xfem_def(const ngsx_mesh &M, const XDefo &D, const double *lset, const DeviceData *dd, int dt, const double4 *rv, int nv,
+                           const double4 *ri, int ni, const XTermsDev &X, int64_t nlist, const int32_t *els, const int8_t *xsign,
+                           const double *ratio, int accumulate, double *mats, const int32_t *rowslot, cudaStream_t st) {
+  constexpr int ND = H1<DIM, ORDER>::ND, NDG = H1<DIM, DORD>::ND;
+  const size_t smem = XDW * ((size_t)XDQ * ND * 32 + ((size_t)XDQ * ND + XDQ + XDQ * XCO + NDG * DIM) * 8);
+  auto kern = k_xfem_def<DIM, ORDER, DORD>;
+  NGSX_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  const int64_t need = (nlist + XDW - 1) / XDW;
+  const unsigned grid = (unsigned)std::max<int64_t>(1, std::min<int64_t>(need, (int64_t)dd->sm_count * 8));
+  kern<<<grid, XDW * 32, smem, st>>>(M, D, lset, dd->cut_table, dt, rv, nv, ri, ni, X, nlist, els, xsign, ratio, accumulate, mats, rowslot);
+  NGSX_LAUNCH_CHECK();
+  return NGSX_OK;
+}
+
 }  // namespace ngsx
 
 using namespace ngsx;
 
-extern "C" int ngsx_xfem_elmat_h1(const ngsx_mesh *mesh, const double *lset_v, int fe_order, int dt, int intorder, int32_t nterms,
-                                  const ngsx_xterm *h_terms, int64_t nlist, const int32_t *els, const int8_t *xsign, const double *ratio,
-                                  int accumulate, double *mats, void *stream) {
-  NGSX_REQUIRE(mesh && (mesh->dim == 2 || mesh->dim == 3) && mesh->vert && mesh->el2v && lset_v, "xfem_elmat: bad mesh / level set");
-  NGSX_REQUIRE(dt >= 0 && dt <= 2 && nlist >= 0 && nterms >= 0 && (nterms == 0 || h_terms), "xfem_elmat: bad arguments");
-  NGSX_REQUIRE(nlist == 0 || (xsign && ratio && mats), "xfem_elmat: NULL array");
-  if (nterms > XMAXTERMS) { set_error("xfem_elmat: more than 32 product terms"); return NGSX_ERR_UNSUPPORTED; }
-  if (fe_order < 1 || fe_order > 2) { set_error("xfem_elmat: H1 order outside the CUDA path (1, 2); no CPU fallback"); return NGSX_ERR_UNSUPPORTED; }
-  const DeviceData *dd = device_data();
-  if (!dd) return NGSX_ERR_CUDA;
-  const double4 *rv, *ri; int nv, ni;
-  if (!rule_lookup(dd, mesh->dim, intorder, &rv, &nv) || !rule_lookup(dd, mesh->dim - 1, intorder, &ri, &ni)) {
-    set_error("xfem_elmat: integration order beyond the tabulated reference rules");
-    return NGSX_ERR_UNSUPPORTED;
-  }
-  XTermsDev X{};
+static int prepare_xterms(int32_t nterms, const ngsx_xterm *h_terms, XTermsDev &X) {
   X.n = nterms;
   for (int t = 0; t < nterms; t++) {
     const ngsx_xterm &s = h_terms[t];
@@ -398,6 +561,26 @@ extern "C" int ngsx_xfem_elmat_h1(const ngsx_mesh *mesh, const double *lset_v, i
     }
     X.cls[9] = (int8_t)o;
   }
+  return NGSX_OK;
+}
+
+extern "C" int ngsx_xfem_elmat_h1(const ngsx_mesh *mesh, const double *lset_v, int fe_order, int dt, int intorder, int32_t nterms,
+                                  const ngsx_xterm *h_terms, int64_t nlist, const int32_t *els, const int8_t *xsign, const double *ratio,
+                                  int accumulate, double *mats, void *stream) {
+  NGSX_REQUIRE(mesh && (mesh->dim == 2 || mesh->dim == 3) && mesh->vert && mesh->el2v && lset_v, "xfem_elmat: bad mesh / level set");
+  NGSX_REQUIRE(dt >= 0 && dt <= 2 && nlist >= 0 && nterms >= 0 && (nterms == 0 || h_terms), "xfem_elmat: bad arguments");
+  NGSX_REQUIRE(nlist == 0 || (xsign && ratio && mats), "xfem_elmat: NULL array");
+  if (nterms > XMAXTERMS) { set_error("xfem_elmat: more than 32 product terms"); return NGSX_ERR_UNSUPPORTED; }
+  if (fe_order < 1 || fe_order > 2) { set_error("xfem_elmat: H1 order outside the CUDA path (1, 2); no CPU fallback"); return NGSX_ERR_UNSUPPORTED; }
+  const DeviceData *dd = device_data();
+  if (!dd) return NGSX_ERR_CUDA;
+  const double4 *rv, *ri; int nv, ni;
+  if (!rule_lookup(dd, mesh->dim, intorder, &rv, &nv) || !rule_lookup(dd, mesh->dim - 1, intorder, &ri, &ni)) {
+    set_error("xfem_elmat: integration order beyond the tabulated reference rules");
+    return NGSX_ERR_UNSUPPORTED;
+  }
+  XTermsDev X{};
+  if (int rc = prepare_xterms(nterms, h_terms, X)) return rc;
   const int32_t *rowslot = take_packed_output();
   if (nlist == 0) return NGSX_OK;
   cudaStream_t st = as_stream(stream);
@@ -407,5 +590,45 @@ extern "C" int ngsx_xfem_elmat_h1(const ngsx_mesh *mesh, const double *lset_v, i
     case 31: return launch_xfem<3, 1>(*mesh, lset_v, dd, dt, rv, nv, ri, ni, X, nlist, els, xsign, ratio, accumulate, mats, rowslot, st);
     case 32: return launch_xfem<3, 2>(*mesh, lset_v, dd, dt, rv, nv, ri, ni, X, nlist, els, xsign, ratio, accumulate, mats, rowslot, st);
   }
+  return NGSX_ERR_UNSUPPORTED;
+}
+
+extern "C" int ngsx_xfem_elmat_h1_deformed(const ngsx_mesh *mesh, const ngsx_deformation *defo, const double *lset_v, int fe_order, int dt,
+                                           int intorder, int32_t nterms, const ngsx_xterm *h_terms, int64_t nlist, const int32_t *els,
+                                           const int8_t *xsign, const double *ratio, int accumulate, double *mats, void *stream) {
+  NGSX_REQUIRE(mesh && (mesh->dim == 2 || mesh->dim == 3) && mesh->vert && mesh->el2v && lset_v, "xfem_elmat_deformed: bad mesh / level set");
+  NGSX_REQUIRE(defo && defo->el2dof && defo->coef, "xfem_elmat_deformed: bad deformation");
+  NGSX_REQUIRE(dt >= 0 && dt <= 2 && nlist >= 0 && nterms >= 0 && (nterms == 0 || h_terms), "xfem_elmat_deformed: bad arguments");
+  NGSX_REQUIRE(nlist == 0 || (xsign && ratio && mats), "xfem_elmat_deformed: NULL array");
+  if (nterms > XMAXTERMS) { set_error("xfem_elmat_deformed: more than 32 product terms"); return NGSX_ERR_UNSUPPORTED; }
+  if (fe_order < 1 || fe_order > 2 || defo->order < 1 || defo->order > 2) {
+    set_error("xfem_elmat_deformed: H1 / deformation order outside the CUDA path (1, 2); no CPU fallback");
+    return NGSX_ERR_UNSUPPORTED;
+  }
+  const DeviceData *dd = device_data();
+  if (!dd) return NGSX_ERR_CUDA;
+  const double4 *rv, *ri; int nv, ni;
+  if (!rule_lookup(dd, mesh->dim, intorder, &rv, &nv) || !rule_lookup(dd, mesh->dim - 1, intorder, &ri, &ni)) {
+    set_error("xfem_elmat_deformed: integration order beyond the tabulated reference rules");
+    return NGSX_ERR_UNSUPPORTED;
+  }
+  XTermsDev X{};
+  if (int rc = prepare_xterms(nterms, h_terms, X)) return rc;
+  const int32_t *rowslot = take_packed_output();
+  if (nlist == 0) return NGSX_OK;
+  cudaStream_t st = as_stream(stream);
+  const XDefo D{defo->el2dof, defo->coef};
+#define XDEF(DIM, ORD, DORD) launch_xfem_def<DIM, ORD, DORD>(*mesh, D, lset_v, dd, dt, rv, nv, ri, ni, X, nlist, els, xsign, ratio, accumulate, mats, rowslot, st)
+  switch (mesh->dim * 100 + fe_order * 10 + defo->order) {
+    case 211: return XDEF(2, 1, 1);
+    case 212: return XDEF(2, 1, 2);
+    case 221: return XDEF(2, 2, 1);
+    case 222: return XDEF(2, 2, 2);
+    case 311: return XDEF(3, 1, 1);
+    case 312: return XDEF(3, 1, 2);
+    case 321: return XDEF(3, 2, 1);
+    case 322: return XDEF(3, 2, 2);
+  }
+#undef XDEF
   return NGSX_ERR_UNSUPPORTED;
 }

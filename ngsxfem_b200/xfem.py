@@ -366,8 +366,6 @@ class SymbolicCutBFI:
         self.xterms = None
         from . import xfes
         if xfes.has_x_atoms(form):
-            if deformation is not None:
-                raise NgsxError(-2, "a deformation on a compound [Vh, XFESpace] integrator is outside the CUDA path")
             self._init_x(form, xfes)
             return
         terms = form.collect()
@@ -769,9 +767,9 @@ class BilinearForm:
             for integ in self.integrators:                         # what the deformed path covers
                 if isinstance(integ, SymbolicFacetPatchBFI):
                     continue
-                if integ.xterms is not None or self.assembly != "rows":
-                    raise NgsxError(-2, "on a deformed mesh SymbolicCutBFI integrators on H1 through the row gather and facet patches are on "
-                                        "the CUDA path (XFESpace and the coloured scatter: undeformed only); no CPU fallback")
+                if integ.xterms is None and self.assembly != "rows":
+                    raise NgsxError(-2, "on a deformed mesh the row gather is the CUDA path (the coloured scatter is undeformed only); "
+                                        "no CPU fallback")
         plans = [self._plan_for(k, integ) for k, integ in enumerate(self.integrators)]
         # a single row plan that covers every stored entry overwrites its rows: no SetZero pass, each value written once
         # (with a row range: the rank's rows are one contiguous CSR span, the other rows belong to other ranks and stay untouched)
@@ -880,16 +878,30 @@ class BilinearForm:
         lv = _lset_vec(integ.lset)
         io = integ.intorder(h1.order)
         mesh_c = ctypes.byref(fes.mesh.c_struct())
+        gfd = self._deformation_of(integ)
+        defo = fes.mesh.c_deformation(gfd) if gfd is not None else None
         if plan.plan_a is not None:
             pa = plan.plan_a
-            check(L.ngsx_assemble_csr_rows_h1(mesh_c, _ptr(lv), h1.order, integ.dt, io, ctypes.byref(integ.form), pa.els.numel(), _ptr(pa.els),
-                                              pa.handle, 1, _ptr(self.mat.vals), _ptr(self._err[k]), _stream()))
+            if defo is not None:                                       # deformed mesh: dense blocks with per-point geometry, packed rows
+                slots, rows = _packed_rows(pa, h1.nd)
+                L.ngsx_set_packed_output(slots)
+                check(L.ngsx_elmat_h1_deformed(mesh_c, ctypes.byref(defo), _ptr(lv), h1.order, integ.dt, io, ctypes.byref(integ.form),
+                                               pa.els.numel(), _ptr(pa.els), _ptr(rows), None, _ptr(self._err[k]), _stream()))
+                check(L.ngsx_assemble_csr_rows_packed(pa.handle, _ptr(rows), 1, _ptr(self.mat.vals), _stream()))
+            else:
+                check(L.ngsx_assemble_csr_rows_h1(mesh_c, _ptr(lv), h1.order, integ.dt, io, ctypes.byref(integ.form), pa.els.numel(), _ptr(pa.els),
+                                                  pa.handle, 1, _ptr(self.mat.vals), _ptr(self._err[k]), _stream()))
             self._err_armed = True
         n = plan.els.numel()
         if n:
             L.ngsx_set_packed_output(plan.shared.slots)
-            check(L.ngsx_xfem_elmat_h1(mesh_c, _ptr(lv), h1.order, integ.dt, io, len(integ.xterms), plan.xterms, n, _ptr(plan.els),
-                                       _ptr(fes.x.xsign), _ptr(fes.x.cutinfo.ratio), 1 if x_blocks else 0, _ptr(plan.mats), _stream()))
+            if defo is not None:
+                check(L.ngsx_xfem_elmat_h1_deformed(mesh_c, ctypes.byref(defo), _ptr(lv), h1.order, integ.dt, io, len(integ.xterms), plan.xterms,
+                                                    n, _ptr(plan.els), _ptr(fes.x.xsign), _ptr(fes.x.cutinfo.ratio), 1 if x_blocks else 0,
+                                                    _ptr(plan.mats), _stream()))
+            else:
+                check(L.ngsx_xfem_elmat_h1(mesh_c, _ptr(lv), h1.order, integ.dt, io, len(integ.xterms), plan.xterms, n, _ptr(plan.els),
+                                           _ptr(fes.x.xsign), _ptr(fes.x.cutinfo.ratio), 1 if x_blocks else 0, _ptr(plan.mats), _stream()))
             return 1
         return 0
 
@@ -1012,9 +1024,9 @@ class LinearForm:
         for k, integ in enumerate(self.integrators):
             gfd = integ.deformation if getattr(integ, "deformation", None) is not None else fes.mesh.deformation
             if gfd is not None:
-                if integ.has_x:
-                    raise NgsxError(-2, "neg / pos test functions on a deformed mesh are outside the CUDA path; no CPU fallback")
                 self._assemble_deformed(integ, k, gfd)
+                if integ.has_x:
+                    self._assemble_x(integ, k, gfd)
                 continue
             if integ.blocks[0] != 0.0:
                 els, dofptr, pairs, elvecs = self._gather_plan(("h1", k), integ)
@@ -1042,7 +1054,7 @@ class LinearForm:
                                        integ.intorder(fes.order), ctypes.byref(poly), els.numel(), _ptr(els), _ptr(elvecs), None, None, _stream()))
         check(L.ngsx_gather_vec(fes.ndof, _ptr(dofptr), _ptr(pairs), _ptr(elvecs), 1.0, 1, _ptr(self.vec), _stream()))
 
-    def _assemble_x(self, integ, k):
+    def _assemble_x(self, integ, k, gfd=None):
         """x-dof part (DiffOpX<RNEG/RPOS> as test operator, xfem/xfemdiffops.cpp:30-40): the element vectors of the IF elements
         (the only ones with x-dofs), gathered per x-dof over the entries whose sign matches the operator -- fixed order, no atomics"""
         L = _lib_()
@@ -1068,8 +1080,14 @@ class LinearForm:
         if x.if_els.numel() == 0:
             return
         poly = _poly_of(integ.poly)
-        check(L.ngsx_elvec_h1(ctypes.byref(fes.mesh.c_struct()), _ptr(_lset_vec(integ.lset)), fes.order, integ.dt, integ.intorder(fes.order),
-                              ctypes.byref(poly), x.if_els.numel(), _ptr(x.if_els), _ptr(elvecs), None, _stream()))
+        if gfd is not None:                                                # deformed mesh: shapes at the reference points, f at the mapped ones
+            defo = fes.mesh.c_deformation(gfd)
+            check(L.ngsx_elvec_h1_deformed(ctypes.byref(fes.mesh.c_struct()), ctypes.byref(defo), _ptr(_lset_vec(integ.lset)), fes.order, integ.dt,
+                                           integ.intorder(fes.order), ctypes.byref(poly), x.if_els.numel(), _ptr(x.if_els), _ptr(elvecs), None, None,
+                                           _stream()))
+        else:
+            check(L.ngsx_elvec_h1(ctypes.byref(fes.mesh.c_struct()), _ptr(_lset_vec(integ.lset)), fes.order, integ.dt, integ.intorder(fes.order),
+                                  ctypes.byref(poly), x.if_els.numel(), _ptr(x.if_els), _ptr(elvecs), None, _stream()))
         xvec = self.vec[fes.ndof:]
         for scale, dofptr, pairs in plans:
             check(L.ngsx_gather_vec(x.ndof, _ptr(dofptr), _ptr(pairs), _ptr(elvecs), float(scale), 1, _ptr(xvec), _stream()))

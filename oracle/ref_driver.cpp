@@ -453,7 +453,7 @@ struct XB
 // (order 2p), stab = stab_factor (alpha0+alpha1)/h, avgflux = -sum_k kappa_k alpha_k grad u_k . n, kappa = (ratio, 1-ratio).
 // xsign == nullptr: uncut element (no x-dofs): the nd x nd block of the std dofs.  elmat (2nd)x(2nd) (or nd x nd) row-major.
 template <ELEMENT_TYPE ET>
-int NxfemElmat(int fe_order, const int * vnums, const double * pmat, const double * lset, const signed char * xsign,
+int NxfemElmat(int fe_order, int dord, const int * vnums, const double * pmat, const double * lset, const signed char * xsign,
                double kappa_neg, double alpha0, double alpha1, double stab_factor, double * elmat_out, LocalHeap & lh)
 {
   constexpr int D = ET_trait<ET>::DIM;
@@ -464,7 +464,7 @@ int NxfemElmat(int fe_order, const int * vnums, const double * pmat, const doubl
   for (int i = 0; i < nd; i++) signs[i] = xsign ? DOMAIN_TYPE(xsign[i]) : IF;      // IF matches neither RNEG nor RPOS: zero x-part
   XFiniteElement xfe(fel, signs, lh);
   XB<ET> xb;
-  auto trafo = MakeTrafo<ET>(0, pmat, lh);
+  auto trafo = MakeTrafo<ET>(dord, pmat, lh);
   Vector<> lv(D+1);
   for (int i = 0; i < D+1; i++) lv(i) = lset[i];
   FlatMatrix<> A(n2, n2, lh); A = 0.0;
@@ -515,7 +515,7 @@ int NxfemElmat(int fe_order, const int * vnums, const double * pmat, const doubl
 
 // SymbolicLFI(levelset_domain = dt, form = f (v_std + op(v_x))), op = neg (dt NEG) / pos (dt POS), py_tutorials/nxfem.py:109-110
 template <ELEMENT_TYPE ET>
-int NxfemElvec(int fe_order, const int * vnums, const double * pmat, const double * lset, const signed char * xsign, int dt,
+int NxfemElvec(int fe_order, int dord, const int * vnums, const double * pmat, const double * lset, const signed char * xsign, int dt,
                int nmono, const double * mono, double * elvec_out, LocalHeap & lh)
 {
   constexpr int D = ET_trait<ET>::DIM;
@@ -526,7 +526,7 @@ int NxfemElvec(int fe_order, const int * vnums, const double * pmat, const doubl
   for (int i = 0; i < nd; i++) signs[i] = xsign ? DOMAIN_TYPE(xsign[i]) : IF;
   XFiniteElement xfe(fel, signs, lh);
   XB<ET> xb;
-  auto trafo = MakeTrafo<ET>(0, pmat, lh);
+  auto trafo = MakeTrafo<ET>(dord, pmat, lh);
   Vector<> lv(D+1);
   for (int i = 0; i < D+1; i++) lv(i) = lset[i];
   const IntegrationRule * ir = StraightCutIntegrationRule(lv, *trafo, DOMAIN_TYPE(dt), 2*fe_order, FIND_OPTIMAL, lh);
@@ -897,24 +897,25 @@ int ref_facetpatch_elmat_h1(int et, int fe_order, int dord, const int * vn1, con
   } catch (...) { return -2; }
 }
 
-int ref_nxfem_elmat(int et, int fe_order, const int * vnums, const double * pmat, const double * lset, const signed char * xsign,
+// dord == 0: affine element, geom = vertex matrix; dord >= 1: isoparametric element of that order, geom = geometry coefficients
+int ref_nxfem_elmat(int et, int fe_order, int dord, const int * vnums, const double * pmat, const double * lset, const signed char * xsign,
                     double kappa_neg, double alpha0, double alpha1, double stab_factor, double * elmat)
 {
   LocalHeap & lh = GetLH(); HeapReset hr(lh);
   try {
-    if (et == ET_TRIG) return NxfemElmat<ET_TRIG>(fe_order, vnums, pmat, lset, xsign, kappa_neg, alpha0, alpha1, stab_factor, elmat, lh);
-    if (et == ET_TET) return NxfemElmat<ET_TET>(fe_order, vnums, pmat, lset, xsign, kappa_neg, alpha0, alpha1, stab_factor, elmat, lh);
+    if (et == ET_TRIG) return NxfemElmat<ET_TRIG>(fe_order, dord, vnums, pmat, lset, xsign, kappa_neg, alpha0, alpha1, stab_factor, elmat, lh);
+    if (et == ET_TET) return NxfemElmat<ET_TET>(fe_order, dord, vnums, pmat, lset, xsign, kappa_neg, alpha0, alpha1, stab_factor, elmat, lh);
     return -4;
   } catch (...) { return -2; }
 }
 
-int ref_nxfem_elvec(int et, int fe_order, const int * vnums, const double * pmat, const double * lset, const signed char * xsign, int dt,
+int ref_nxfem_elvec(int et, int fe_order, int dord, const int * vnums, const double * pmat, const double * lset, const signed char * xsign, int dt,
                     int nmono, const double * mono, double * elvec)
 {
   LocalHeap & lh = GetLH(); HeapReset hr(lh);
   try {
-    if (et == ET_TRIG) return NxfemElvec<ET_TRIG>(fe_order, vnums, pmat, lset, xsign, dt, nmono, mono, elvec, lh);
-    if (et == ET_TET) return NxfemElvec<ET_TET>(fe_order, vnums, pmat, lset, xsign, dt, nmono, mono, elvec, lh);
+    if (et == ET_TRIG) return NxfemElvec<ET_TRIG>(fe_order, dord, vnums, pmat, lset, xsign, dt, nmono, mono, elvec, lh);
+    if (et == ET_TET) return NxfemElvec<ET_TET>(fe_order, dord, vnums, pmat, lset, xsign, dt, nmono, mono, elvec, lh);
     return -4;
   } catch (...) { return -2; }
 }

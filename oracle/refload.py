@@ -61,7 +61,7 @@ def load():
     sp = ctypes.POINTER(ctypes.c_byte)
     L.ref_elmat_h1_form.argtypes = [c_int, c_int, c_int, ip, dp, dp, c_int, c_int, dp, dp]
     L.ref_facetpatch_elmat_h1.argtypes = [c_int, c_int, c_int, ip, dp, ip, dp, c_double, c_int, dp, dp]
-    L.ref_nxfem_elmat.argtypes = [c_int, c_int, ip, dp, dp, sp, c_double, c_double, c_double, c_double, dp]
-    L.ref_nxfem_elvec.argtypes = [c_int, c_int, ip, dp, dp, sp, c_int, c_int, dp, dp]
+    L.ref_nxfem_elmat.argtypes = [c_int, c_int, c_int, ip, dp, dp, sp, c_double, c_double, c_double, c_double, dp]
+    L.ref_nxfem_elvec.argtypes = [c_int, c_int, c_int, ip, dp, dp, sp, c_int, c_int, dp, dp]
     _LIB = L
     return L

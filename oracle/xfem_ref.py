@@ -102,7 +102,8 @@ def nxfem_elvec(dim, order, vnums, pmat, ls, xsign, dt, fpoly):
 # the same two functions through the reference's own DiffOpX / XFiniteElement (oracle/_ref, ref_driver.cpp:NxfemElmat):
 # what pins the numpy restatement above (tests/test_oracle_vs_ref.py::test_xfem_*)
 # ---------------------------------------------------------------------------------------------------------------------
-def nxfem_elmat_ref(dim, order, vnums, pmat, ls, xsign, kappa_neg, alpha, stab_factor):
+def nxfem_elmat_ref(dim, order, vnums, pmat, ls, xsign, kappa_neg, alpha, stab_factor, dord=0):
+    """dord >= 1: pmat = geometry coefficients of the isoparametric element of that order (deformed mesh)"""
     import ctypes
     from . import refload
     L = refload.load()
@@ -113,12 +114,12 @@ def nxfem_elmat_ref(dim, order, vnums, pmat, ls, xsign, kappa_neg, alpha, stab_f
     l = np.ascontiguousarray(ls, dtype=np.float64)
     xs = None if xsign is None else np.ascontiguousarray(xsign, dtype=np.int8)
     xp = None if xs is None else xs.ctypes.data_as(ctypes.POINTER(ctypes.c_byte))
-    r = L.ref_nxfem_elmat(orc.ET[dim], order, orc.P(vn, orc.ip), orc.P(pm), orc.P(l), xp, kappa_neg, alpha[0], alpha[1], stab_factor, orc.P(em))
+    r = L.ref_nxfem_elmat(orc.ET[dim], order, dord, orc.P(vn, orc.ip), orc.P(pm), orc.P(l), xp, kappa_neg, alpha[0], alpha[1], stab_factor, orc.P(em))
     assert r >= 0, r
     return em
 
 
-def nxfem_elvec_ref(dim, order, vnums, pmat, ls, xsign, dt, fpoly):
+def nxfem_elvec_ref(dim, order, vnums, pmat, ls, xsign, dt, fpoly, dord=0):
     import ctypes
     from . import refload
     L = refload.load()
@@ -130,5 +131,5 @@ def nxfem_elvec_ref(dim, order, vnums, pmat, ls, xsign, dt, fpoly):
     xs = None if xsign is None else np.ascontiguousarray(xsign, dtype=np.int8)
     xp = None if xs is None else xs.ctypes.data_as(ctypes.POINTER(ctypes.c_byte))
     mono = orc.mono_array([(c, e[0], e[1], e[2]) for e, c in fpoly.items()])
-    L.ref_nxfem_elvec(orc.ET[dim], order, orc.P(vn, orc.ip), orc.P(pm), orc.P(l), xp, dt, len(mono), orc.P(mono), orc.P(ev))
+    L.ref_nxfem_elvec(orc.ET[dim], order, dord, orc.P(vn, orc.ip), orc.P(pm), orc.P(l), xp, dt, len(mono), orc.P(mono), orc.P(ev))
     return ev

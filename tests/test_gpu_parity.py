@@ -1755,3 +1755,90 @@ def test_deformed_facet_patches_against_oracle(X, dim, fo, dord):
     c += xf.SymbolicFacetPatchBFI(form=0.1 * 1.0 / h * 1.0 / h * (u - u.Other()) * (v - v.Other()), skeleton=False, definedonelements=ba)
     c.Assemble()
     assert (b.mat.vals - c.mat.vals).abs().max().item() <= 1e-11 * c.mat.vals.abs().max().item()
+
+
+@pytest.mark.parametrize("dim,fo,dord", [(2, 1, 1), (2, 2, 2), (3, 1, 2), (3, 2, 2)])
+def test_deformed_xfem_compound_operator(X, dim, fo, dord):
+    """row f-4: the two-phase Nitsche-XFEM operator and right-hand side of py_tutorials/nxfem.py:62-110 on a DEFORMED mesh
+    (mesh.SetDeformation as in nxfem_higher_order.py): against the reference's own DiffOpX / XFiniteElement on isoparametric
+    transformations (oracle/_ref: ref_nxfem_elmat / ref_nxfem_elvec), and a zero deformation against the affine path"""
+    from oracle import refload, xfem_ref
+    import scipy.sparse as sp
+    xf, ngs = X.xfem, X.ngs
+    mesh, gf, defo, Vd = _deformed_setup(X, dim, dord, amp=0.06)
+    ci = xf.CutInfo(mesh, gf)
+    Vh = ngs.H1(mesh, order=fo)
+    Vhx = xf.XFESpace(Vh, ci)
+    from ngsxfem_b200.xfes import FESpace
+    VhG = FESpace([Vh, Vhx])
+    alpha = [1.0, 2.0]
+    n = ngs.LevelsetNormal(gf)
+    h = ngs.specialcf.mesh_size
+    kappa = (xf.CutRatioGF(ci), 1.0 - xf.CutRatioGF(ci))
+    stab = 20 * (alpha[1] + alpha[0]) / h
+    (u_std, u_x), (v_std, v_x) = VhG.TrialFunction(), VhG.TestFunction()
+    u = [u_std + op(u_x) for op in (xf.neg, xf.pos)]
+    v = [v_std + op(v_x) for op in (xf.neg, xf.pos)]
+    gradu = [ngs.grad(u_std) + op(u_x) for op in (xf.neg_grad, xf.pos_grad)]
+    gradv = [ngs.grad(v_std) + op(v_x) for op in (xf.neg_grad, xf.pos_grad)]
+    flux_u = sum([-kappa[i] * alpha[i] * gradu[i] * n for i in (0, 1)])
+    flux_v = sum([-kappa[i] * alpha[i] * gradv[i] * n for i in (0, 1)])
+    fp = {(0, 0, 0): 1.0, (1, 0, 0): 0.5, (0, 1, 0): -0.25}
+    fcf = 1.0 + 0.5 * ngs.x - 0.25 * ngs.y
+
+    def build():
+        a = xf.BilinearForm(VhG)
+        a += xf.SymbolicBFI(levelset_domain={"levelset": gf, "domain_type": NEG}, form=alpha[0] * gradu[0] * gradv[0])
+        a += xf.SymbolicBFI(levelset_domain={"levelset": gf, "domain_type": POS}, form=alpha[1] * gradu[1] * gradv[1])
+        a += xf.SymbolicBFI(levelset_domain={"levelset": gf, "domain_type": IF},
+                            form=flux_u * (v[0] - v[1]) + flux_v * (u[0] - u[1]) + stab * (u[0] - u[1]) * (v[0] - v[1]))
+        f = xf.LinearForm(VhG)
+        f += xf.SymbolicLFI(levelset_domain={"levelset": gf, "domain_type": NEG}, form=fcf * v[0])
+        f += xf.SymbolicLFI(levelset_domain={"levelset": gf, "domain_type": POS}, form=fcf * v[1])
+        return a, f
+
+    # zero deformation == affine
+    a0, f0 = build()
+    a0.Assemble(); f0.Assemble()
+    mesh.SetDeformation(ngs.GridFunction(Vd))
+    az, fz = build()
+    az.Assemble(); fz.Assemble()
+    assert_csr_close(az.mat.vals, a0.mat.vals, a0.mat.rowptr, 1e-11)
+    assert (fz.vec - f0.vec).abs().max().item() <= 1e-12 * f0.vec.abs().max().item()
+    # the deformed operator
+    mesh.SetDeformation(defo)
+    a, f = build()
+    a.Assemble(); f.Assemble()
+    first, fv = a.mat.vals.clone(), f.vec.clone()
+    a.mat.vals.fill_(float("nan"))
+    a.Assemble(); f.Assemble()
+    assert torch.equal(first, a.mat.vals) and torch.equal(fv, f.vec)           # bitwise reproducible
+    assert (first - a0.mat.vals).abs().max().item() > 1e-6 * a0.mat.vals.abs().max().item()
+    mesh.UnsetDeformation()
+    if not refload.available():
+        pytest.skip("oracle/_ref not built: the deformed blocks are pinned against the compiled reference only")
+    el2v, vert, ls, e2d = mesh.el2v.cpu().numpy(), mesh.vert.cpu().numpy(), gf.vec.cpu().numpy(), Vh.el2dof.cpu().numpy()
+    e2dd, dv = Vd.el2dof.cpu().numpy(), defo.vec.cpu().numpy()
+    dom, ratio = ci.dom.cpu().numpy(), ci.ratio.cpu().numpy()
+    b2x, dod = Vhx.basedof2xdof.cpu().numpy(), Vhx.domofdof.cpu().numpy()
+    A = sp.lil_matrix((VhG.ndof, VhG.ndof))
+    rhs = np.zeros(VhG.ndof)
+    for e in range(mesh.ne):
+        g = dv[e2dd[e]].copy()
+        g[: dim + 1] += vert[el2v[e]]
+        l = ls[el2v[e]]
+        if dom[e] == 2:
+            xs = dod[b2x[e2d[e]]]
+            d = np.concatenate([e2d[e], Vh.ndof + b2x[e2d[e]]])
+        else:
+            xs, d = None, e2d[e]
+        em = xfem_ref.nxfem_elmat_ref(dim, fo, el2v[e], g, l, xs, ratio[e], alpha, 20.0, dord=dord)
+        ev = xfem_ref.nxfem_elvec_ref(dim, fo, el2v[e], g, l, xs, 0, fp, dord=dord) + xfem_ref.nxfem_elvec_ref(dim, fo, el2v[e], g, l, xs, 1, fp, dord=dord)
+        rhs[d] += ev
+        for i in range(len(d)):
+            for j in range(len(d)):
+                A[d[i], d[j]] += em[i, j]
+    ref = A.tocsr()
+    got = sp.csr_matrix((first.cpu().numpy(), a.mat.colidx.cpu().numpy(), a.mat.rowptr.cpu().numpy()), shape=ref.shape)
+    assert abs(got - ref).max() <= 1e-11 * abs(ref).max()
+    assert np.abs(fv.cpu().numpy() - rhs).max() <= 1e-12 * np.abs(rhs).max()
