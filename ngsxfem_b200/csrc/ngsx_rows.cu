@@ -303,6 +303,12 @@ __device__ __forceinline__ void row_values_cut(const double *cm, double *v) {
   }
 }
 
+// the 128-byte line of a pair's geometry record(s) into L1, two steps before load_geo reads it
+template <int DIM>
+__device__ __forceinline__ void prefetch_geo(const RowArgs &A, uint32_t w0) {
+  prefetch_l1(A.G + (int64_t)(w0 & DESC_KMASK) * ((DIM + 1) * 4));
+}
+
 // geometry record(s) of a pair: vertex row i -> record i; edge row (a, b) -> records a and b (the same 128-byte line)
 template <int DIM, int ORDER>
 __device__ __forceinline__ void load_geo(const RowArgs &A, uint32_t w0, double *ga, double *gb) {
@@ -322,7 +328,8 @@ __device__ __forceinline__ void load_geo(const RowArgs &A, uint32_t w0, double *
 // WARP = one tile of consecutive CSR rows whose values (<= ACCW doubles) live in the warp's private shared-memory window:
 // initialised by the warp (zero, or the current values when accumulating), gathered, and streamed out once with coalesced
 // stores.  Warps never wait for each other.  LANE = the rows the schedule dealt to it: per step one (row, element) pair --
-// descriptor (prefetched two steps ahead, coalesced), geometry record(s) (one step ahead), closed-form row, nd window adds.
+// descriptor (the tile's block prefetched into L2 at tile start, registers three steps ahead, coalesced), geometry record(s)
+// (L1 prefetch two steps ahead, registers one step ahead), closed-form row, nd window adds.
 // No two lanes share a row and the nd columns of one element are distinct, so every CSR entry is summed in plan order.
 template <int DIM, int ORDER>
 __global__ void __launch_bounds__(RW * 32, NGSX_MINBLOCKS) k_rows(RowArgs A) {
@@ -337,15 +344,20 @@ __global__ void __launch_bounds__(RW * 32, NGSX_MINBLOCKS) k_rows(RowArgs A) {
     const int64_t z0 = __ldg(&H->z0);
     const int zlen = __ldg(&H->zlen), nsteps = __ldg(&H->nsteps);
     const int myload = __ldg(&H->load[lane]);
-    int64_t base2 = __ldg(&H->d0);
-    // prime the pipeline: descriptors of steps 0 and 1, geometry of step 0
-    uint4 dcur = null4, dnext = null4;
-    if (0 < myload) dcur = __ldg(A.desc + base2 + lane);
-    base2 += __popc(__ballot_sync(0xffffffffu, 0 < myload));
-    if (1 < myload) dnext = __ldg(A.desc + base2 + lane);
-    base2 += __popc(__ballot_sync(0xffffffffu, 1 < myload));
+    int64_t base3 = __ldg(&H->d0);
+    prefetch_block_l2(A.desc, base3, __reduce_add_sync(0xffffffffu, myload), 16, lane);
+    if (tt + nwarps < A.ntiles) prefetch_l1(A.tiles + tt + nwarps);             // the next tile's header
+    // prime the pipeline: descriptors of steps 0, 1, 2, geometry of step 0 (registers) and of step 1 (L1)
+    uint4 dcur = null4, dnext = null4, dnext2 = null4;
+    if (0 < myload) dcur = __ldg(A.desc + base3 + lane);
+    base3 += __popc(__ballot_sync(0xffffffffu, 0 < myload));
+    if (1 < myload) dnext = __ldg(A.desc + base3 + lane);
+    base3 += __popc(__ballot_sync(0xffffffffu, 1 < myload));
+    if (2 < myload) dnext2 = __ldg(A.desc + base3 + lane);
+    base3 += __popc(__ballot_sync(0xffffffffu, 2 < myload));
     double ga[4] = {0.0, 0.0, 0.0, 0.0}, gb[4] = {0.0, 0.0, 0.0, 0.0};
     if (0 < myload) load_geo<DIM, ORDER>(A, dcur.x, ga, gb);
+    if (1 < myload) prefetch_geo<DIM>(A, dnext.x);
     if (A.accumulate) for (int t = lane; t < zlen; t += 32) acc[t] = A.vals[z0 + t];
     else for (int t = lane; t < zlen; t += 32) acc[t] = 0.0;
     __syncwarp();
@@ -354,10 +366,11 @@ __global__ void __launch_bounds__(RW * 32, NGSX_MINBLOCKS) k_rows(RowArgs A) {
       double a4[4], b4[4];
 #pragma unroll
       for (int m = 0; m < 4; m++) { a4[m] = ga[m]; b4[m] = gb[m]; }
-      dcur = dnext;
-      if (s + 2 < myload) dnext = __ldg(A.desc + base2 + lane);
-      base2 += __popc(__ballot_sync(0xffffffffu, s + 2 < myload));
+      dcur = dnext; dnext = dnext2;
+      if (s + 3 < myload) dnext2 = __ldg(A.desc + base3 + lane);
+      base3 += __popc(__ballot_sync(0xffffffffu, s + 3 < myload));
       if (s + 1 < myload) load_geo<DIM, ORDER>(A, dcur.x, ga, gb);
+      if (s + 2 < myload) prefetch_geo<DIM>(A, dnext.x);
       if (s < myload) {
         const int i = (int)(d.x >> DESC_KBITS);
         const unsigned long long cb = (unsigned long long)__double_as_longlong(a4[3]);

@@ -78,6 +78,17 @@ constexpr int TILE_MAXPAIRS = NGSX_TILE_MAXPAIRS;
 // s + 1 = row s of cutmats
 constexpr unsigned long long GCODE_NAN = 0x7ff8000000000000ULL;
 
+// software prefetch (no destination register): the schedule is static, so a warp can pull the descriptor block of its tile into
+// L2 when it starts the tile, and the geometry record of a pair into L1 two steps before it is used
+__device__ __forceinline__ void prefetch_l2(const void *p) { asm volatile("prefetch.global.L2 [%0];" ::"l"(p)); }
+__device__ __forceinline__ void prefetch_l1(const void *p) { asm volatile("prefetch.global.L1 [%0];" ::"l"(p)); }
+// the tile's contiguous block of `count` records of `bytes` bytes starting at record d0, 128-byte lines dealt to the lanes
+__device__ __forceinline__ void prefetch_block_l2(const void *base, int64_t d0, int count, int bytes, int lane) {
+  const char *p = reinterpret_cast<const char *>(base) + d0 * bytes;
+  const int total = count * bytes;
+  for (int off = lane * 128; off < total; off += 32 * 128) prefetch_l2(p + off);
+}
+
 int rows_scratch(ngsx_rowplan *plan, int dim);
 int rows_reserve_cut(ngsx_rowplan *plan, int64_t cap);
 // moments of the reference rule of a dim-simplex; false if the rule is not permutation symmetric (or not tabulated)

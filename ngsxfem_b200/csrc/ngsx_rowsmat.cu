@@ -99,6 +99,8 @@ __global__ void __launch_bounds__(RW * 32) k_rows_mats(RowMatArgs A) {
     const int zlen = __ldg(&H->zlen), nsteps = __ldg(&H->nsteps);
     const int myload = __ldg(&H->load[lane]);
     int64_t base = __ldg(&H->d0);
+    prefetch_block_l2(A.desc, base, __reduce_add_sync(0xffffffffu, myload), DS, lane);
+    if (tt + nwarps < A.ntiles) prefetch_l1(A.tiles + tt + nwarps);
     if (A.accumulate) for (int t = lane; t < zlen; t += 32) acc[t] = A.vals[z0 + t];
     else for (int t = lane; t < zlen; t += 32) acc[t] = 0.0;
     Desc<DS> d{};
@@ -152,14 +154,24 @@ __global__ void __launch_bounds__(RW * 32) k_rows_packed(RowMatArgs A) {
     const int zlen = __ldg(&H->zlen), nsteps = __ldg(&H->nsteps);
     const int myload = __ldg(&H->load[lane]);
     int64_t base = __ldg(&H->d0);                                 // slot of (step, lane 0)
+    {                                                             // the tile's descriptors and rows are two contiguous blocks: into L2 now
+      const int tot = __reduce_add_sync(0xffffffffu, myload);
+      prefetch_block_l2(A.desc, base, tot, DS, lane);
+      prefetch_block_l2(A.mats, base, tot, NDP * 8, lane);
+      if (tt + nwarps < A.ntiles) prefetch_l1(A.tiles + tt + nwarps);
+    }
     if (A.accumulate) for (int t = lane; t < zlen; t += 32) acc[t] = A.vals[z0 + t];
     else for (int t = lane; t < zlen; t += 32) acc[t] = 0.0;
-    // the run of step s: cnt(s) rows of NDP doubles at A.mats + base * NDP, i.e. cnt * NC chunks of 16 bytes
-    Desc<DS> d{};
+    // the run of step s: cnt(s) rows of NDP doubles at A.mats + base * NDP, i.e. cnt * NC chunks of 16 bytes.
+    // Registers: descriptors two steps ahead, the run one step ahead.
+    Desc<DS> d{}, dn{};
     uint4 chunk[NC];
     int cnt = __popc(__ballot_sync(0xffffffffu, 0 < myload));
+    int64_t dbase = base + cnt;                                   // descriptor slot of (step 1, lane 0)
     {
       if (0 < myload) d = ld_desc<DS>(A.desc, base + lane);
+      if (1 < myload) dn = ld_desc<DS>(A.desc, dbase + lane);
+      dbase += __popc(__ballot_sync(0xffffffffu, 1 < myload));
       const uint4 *src = reinterpret_cast<const uint4 *>(A.mats + base * NDP);
 #pragma unroll
       for (int c = 0; c < NC; c++) if (lane + 32 * c < cnt * NC) chunk[c] = __ldg(src + lane + 32 * c);
@@ -174,8 +186,10 @@ __global__ void __launch_bounds__(RW * 32) k_rows_packed(RowMatArgs A) {
       }
       base += cnt;
       cnt = __popc(__ballot_sync(0xffffffffu, s + 1 < myload));
-      if (cnt > 0) {                                              // next step's run and descriptors fly during the adds
-        if (s + 1 < myload) d = ld_desc<DS>(A.desc, base + lane);
+      d = dn;
+      if (s + 2 < myload) dn = ld_desc<DS>(A.desc, dbase + lane);
+      dbase += __popc(__ballot_sync(0xffffffffu, s + 2 < myload));
+      if (cnt > 0) {                                              // next step's run flies during the adds
         const uint4 *src = reinterpret_cast<const uint4 *>(A.mats + base * NDP);
 #pragma unroll
         for (int c = 0; c < NC; c++) if (lane + 32 * c < cnt * NC) chunk[c] = __ldg(src + lane + 32 * c);
