@@ -247,6 +247,13 @@ int ngsx_gather_vec(int64_t ndof, const int64_t *dofptr /*[ndof+1]*/, const int6
  * reproducible run to run).  out is a device double. */
 int ngsx_integrate(const ngsx_mesh *mesh, const double *lset_v, int dt, int order, const ngsx_poly *h_f, double *out, void *stream);
 
+/* Fused sweep: ngsx_classify and up to 4 ngsx_integrate calls on the same level set in one pass over the element table
+ * (CutInfo.Update followed by Integrate(...) calls is the usual sequence of a step; each of them alone streams el2v once and has
+ * its own latency floor).  Outputs as ngsx_classify (any may be NULL); integral j over (h_dt[j], h_order[j]) of h_f[j] goes to
+ * out[j] (device).  Bitwise the results of the separate calls: same partial sums, same reduction tree. */
+int ngsx_classify_integrate(const ngsx_mesh *mesh, const double *lset_v, uint32_t *cdom_words, int8_t *dom, double *ratio, int64_t *err,
+                            int32_t nint, const int32_t *h_dt, const int32_t *h_order, const ngsx_poly *h_f, double *out, void *stream);
+
 /* ---- (f-4) deformed (isoparametric) elements -----------------------------------------------------------------------
  * mesh.SetDeformation(gf) (NGS/comp/bilinearform.cpp:1235 picks the deformed ElementTransformation; lsetcurving/lsetcurv.py
  * :108-163 produces gf): x(xi) = affine map + sum_i coef[el2dof[e][i]] phi_i(xi), phi = scalar H1 basis of `order` (1..2,

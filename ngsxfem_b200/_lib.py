@@ -84,6 +84,8 @@ SIGNATURES = {
     "ngsx_rowplan_rowslots": (c_int, [c_void_p, ctypes.POINTER(c_void_p), ctypes.POINTER(c_i64), c_void_p]),
     "ngsx_assemble_csr_rows_packed": (c_int, [c_void_p, c_void_p, c_int, c_void_p, c_void_p]),
     "ngsx_set_packed_output": (None, [c_void_p]),
+    "ngsx_classify_integrate": (c_int, [ctypes.POINTER(Mesh), c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_i32, ctypes.POINTER(c_i32),
+                                        ctypes.POINTER(c_i32), ctypes.POINTER(Poly), c_void_p, c_void_p]),
     "ngsx_xfem_elmat_h1_deformed": (c_int, [ctypes.POINTER(Mesh), ctypes.POINTER(Deformation), c_void_p, c_int, c_int, c_int, c_i32, c_void_p,
                                             c_i64, c_void_p, c_void_p, c_void_p, c_int, c_void_p, c_void_p]),
     "ngsx_facetpatch_cmat_h1_deformed": (c_int, [ctypes.POINTER(Mesh), ctypes.POINTER(Deformation), c_int, ctypes.c_double, c_int, c_i64, c_void_p, c_void_p, c_i32, c_void_p, c_void_p]),

@@ -714,6 +714,181 @@ static void launch_int_cut(bool iface, bool fc, unsigned grid, cudaStream_t st, 
   else { if (fc) k_int_cut<DIM, false, true><<<grid, 256, 0, st>>>(a...); else k_int_cut<DIM, false, false><<<grid, 256, 0, st>>>(a...); }
 }
 
+// ---------------------------------------------------------------------------------------------------------------
+// Fused sweep (ngsx_classify_integrate): CutInfo.Update and up to FUSE_MAXINT Integrate calls on the same level set read the
+// element table ONCE.  Per chunk the warp does what classify_chunk and int_uncut_chunk do -- sign test, the eight bit arrays,
+// domains, cut ratio of the uncut elements, and per integral the static-rule integral of the uncut elements of its domain,
+// summed per word by the same butterfly -- so every partial array is bitwise the one ngsx_integrate builds, and the cut passes
+// (k_classify_cut, k_int_cut) and the reduction tree run unchanged on top of it.  Three 160 MB streams and three latency
+// floors become one (the sweeps are the strong-scaling limiter of the step on a 1/8 mesh).
+// ---------------------------------------------------------------------------------------------------------------
+constexpr int FUSE_MAXINT = 4;
+struct FusedInt {
+  int n;
+  int dt[FUSE_MAXINT], nr_vol[FUSE_MAXINT], fconst[FUSE_MAXINT];
+  const double4 *rule_vol[FUSE_MAXINT];
+  double wref_vol[FUSE_MAXINT];
+  double *partial[FUSE_MAXINT];
+  PolyDev f[FUSE_MAXINT];
+};
+
+template <int DIM, bool FULL>
+__device__ __forceinline__ void fused_chunk(const ngsx_mesh &M, const double *__restrict__ lset, uint32_t *__restrict__ words,
+                                            uint32_t *__restrict__ ifwords, int64_t nwords, int8_t *__restrict__ dom_out,
+                                            double *__restrict__ ratio, unsigned long long *__restrict__ err, const FusedInt &I, int64_t nred,
+                                            int64_t c, int64_t first, int n, const int32_t *stage, int nstaged) {
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  int v[STREAM_WPW][4];
+  double ls[STREAM_WPW][4];
+#pragma unroll
+  for (int k = 0; k < STREAM_WPW; k++) {
+    const int i = (warp * STREAM_WPW + k) * 32 + lane;
+    if (FULL || i < n) stream_vertices<DIM>(stage, FULL ? STREAM_CH : nstaged, M.el2v, first, i, v[k]);
+  }
+#pragma unroll
+  for (int k = 0; k < STREAM_WPW; k++) {
+    const int i = (warp * STREAM_WPW + k) * 32 + lane;
+    if (FULL || i < n) {
+#pragma unroll
+      for (int a = 0; a <= DIM; a++) ls[k][a] = __ldg(lset + v[k][a]);
+    }
+  }
+  unsigned bn[STREAM_WPW], bp[STREAM_WPW], bi[STREAM_WPW], ba[STREAM_WPW];
+  int domk[STREAM_WPW];
+#pragma unroll
+  for (int k = 0; k < STREAM_WPW; k++) {
+    const int i = (warp * STREAM_WPW + k) * 32 + lane;
+    const int64_t e = first + i;
+    int dom = -2;                                    // -2: beyond ne
+    if (FULL || i < n) {
+      int mask;
+      dom = sign_test<DIM>(ls[k], mask);
+      if (ratio && dom != IF) ratio[e] = dom == NEG ? 1.0 : (dom == POS ? 0.0 : nan(""));
+      if (dom_out) dom_out[e] = (int8_t)dom;
+      if (dom == -1 && err) {
+        atomicAdd(&err[0], 1ULL);
+        atomicMin(reinterpret_cast<long long *>(&err[1]), (long long)e);
+      }
+    }
+    domk[k] = dom;
+    bn[k] = __ballot_sync(0xffffffffu, dom == NEG); bp[k] = __ballot_sync(0xffffffffu, dom == POS);
+    bi[k] = __ballot_sync(0xffffffffu, dom == IF); ba[k] = __ballot_sync(0xffffffffu, dom != -2);
+  }
+  {
+    const int kk = lane & 3, arr = lane >> 2;
+    const unsigned n_ = kk == 0 ? bn[0] : kk == 1 ? bn[1] : kk == 2 ? bn[2] : bn[3];
+    const unsigned p_ = kk == 0 ? bp[0] : kk == 1 ? bp[1] : kk == 2 ? bp[2] : bp[3];
+    const unsigned i_ = kk == 0 ? bi[0] : kk == 1 ? bi[1] : kk == 2 ? bi[2] : bi[3];
+    const unsigned a_ = kk == 0 ? ba[0] : kk == 1 ? ba[1] : kk == 2 ? ba[2] : ba[3];
+    const unsigned sel = arr == NGSX_CDOM_ANY ? a_ : (((arr & 1) ? n_ : 0u) | ((arr & 2) ? p_ : 0u) | ((arr & 4) ? i_ : 0u));
+    const int64_t w = c * (STREAM_CH / 32) + warp * STREAM_WPW + kk;
+    if (w < nwords) {
+      if (words) words[arr * nwords + w] = sel;
+      if (ifwords && arr == NGSX_CDOM_IF) ifwords[w] = sel;
+    }
+  }
+  // the uncut parts of the integrals (as int_uncut_chunk)
+  double val[FUSE_MAXINT][STREAM_WPW];
+#pragma unroll
+  for (int j = 0; j < FUSE_MAXINT; j++)
+#pragma unroll
+    for (int k = 0; k < STREAM_WPW; k++) val[j][k] = 0.0;
+#pragma unroll
+  for (int k = 0; k < STREAM_WPW; k++) {
+    const int dom = domk[k];
+    bool need = false;
+#pragma unroll
+    for (int j = 0; j < FUSE_MAXINT; j++) need |= j < I.n && dom == I.dt[j] && dom != IF;
+    if (need) {
+      double p[DIM + 1][DIM];
+#pragma unroll
+      for (int a = 0; a <= DIM; a++)
+#pragma unroll
+        for (int d = 0; d < DIM; d++) p[a][d] = __ldg(M.vert + (int64_t)v[k][a] * DIM + d);
+      ElGeom<DIM> G;
+      element_geometry<DIM>(p, G);
+      const double meas = fabs(G.det);
+#pragma unroll
+      for (int j = 0; j < FUSE_MAXINT; j++) {
+        if (j < I.n && dom == I.dt[j]) {
+          if (I.fconst[j]) {
+            val[j][k] = meas * (I.wref_vol[j] * I.f[j].c[0]);
+          } else {
+            double sum = 0.0;
+            for (int q = 0; q < I.nr_vol[j]; q++) {
+              const double4 r = I.rule_vol[j][q];
+              double xi[3] = {r.x, r.y, r.z}, x[3];
+              map_point<DIM>(p, xi, x);
+              sum += meas * r.w * eval_poly(I.f[j], x);
+            }
+            val[j][k] = sum;
+          }
+        }
+      }
+    }
+  }
+#pragma unroll
+  for (int j = 0; j < FUSE_MAXINT; j++) {
+    if (j < I.n) {
+#pragma unroll
+      for (int k = 0; k < STREAM_WPW; k++) {
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) val[j][k] += __shfl_xor_sync(0xffffffffu, val[j][k], o);
+      }
+      if (lane < STREAM_WPW) {
+        const int64_t w = c * (STREAM_CH / 32) + warp * STREAM_WPW + lane;
+        if (w < nred) I.partial[j][w] = lane == 0 ? val[j][0] : lane == 1 ? val[j][1] : lane == 2 ? val[j][2] : val[j][3];
+      }
+    }
+  }
+}
+
+template <int DIM>
+__global__ void __launch_bounds__(STREAM_THREADS, 2) k_fused_sweep(ngsx_mesh M, const double *__restrict__ lset, uint32_t *__restrict__ words,
+                                                                  uint32_t *__restrict__ ifwords, int64_t nwords, int8_t *__restrict__ dom_out,
+                                                                  double *__restrict__ ratio, unsigned long long *__restrict__ err,
+                                                                  const __grid_constant__ FusedInt I, int64_t nred) {
+  extern __shared__ __align__(128) unsigned char smem_stream[];
+  stream_elements<DIM>(M, smem_stream, [&](int64_t c, int64_t first, int n, const int32_t *stage, int nstaged) {
+    if (n == STREAM_CH && nstaged == STREAM_CH) fused_chunk<DIM, true>(M, lset, words, ifwords, nwords, dom_out, ratio, err, I, nred, c, first, n, stage, nstaged);
+    else fused_chunk<DIM, false>(M, lset, words, ifwords, nwords, dom_out, ratio, err, I, nred, c, first, n, stage, nstaged);
+  });
+  const int64_t wend = ((M.ne + STREAM_CH - 1) / STREAM_CH) * (STREAM_CH / 32);
+  if (blockIdx.x == 0)
+    for (int j = 0; j < I.n; j++)
+      for (int64_t w = wend + threadIdx.x; w < nred; w += blockDim.x) I.partial[j][w] = 0.0;
+}
+
+// reduction tree of several integrals at once: blockIdx.y = integral
+__global__ void __launch_bounds__(256) k_int_reduce_multi(int64_t n, int64_t stride, const double *__restrict__ in, double *__restrict__ mid, int nmid) {
+  __shared__ double wsum[8];
+  const double *src = in + (int64_t)blockIdx.y * stride;
+  double sum = 0.0;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) sum += src[i];
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) sum += __shfl_xor_sync(0xffffffffu, sum, o);
+  if ((threadIdx.x & 31) == 0) wsum[threadIdx.x >> 5] = sum;
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    double s = 0.0;
+    for (int w = 0; w < 8; w++) s += wsum[w];
+    mid[(int64_t)blockIdx.y * nmid + blockIdx.x] = s;
+  }
+}
+__global__ void __launch_bounds__(1024) k_reduce_final_multi(int64_t n, const double *__restrict__ mid, double *__restrict__ out) {
+  __shared__ double s[1024];
+  const double *partial = mid + (int64_t)blockIdx.x * n;
+  double acc = 0.0;
+  for (int64_t i = threadIdx.x; i < n; i += 1024) acc += partial[i];
+  s[threadIdx.x] = acc;
+  __syncthreads();
+  for (int o = 512; o > 0; o >>= 1) {
+    if ((int)threadIdx.x < o) s[threadIdx.x] += s[threadIdx.x + o];
+    __syncthreads();
+  }
+  if (threadIdx.x == 0) out[blockIdx.x] = s[0];
+}
+
 // middle level: fixed grid, block-stride over the warp partials, fixed block tree -> one partial per block
 __global__ void __launch_bounds__(256) k_int_reduce(int64_t n, const double *__restrict__ in, double *__restrict__ partial) {
   __shared__ double wsum[8];
@@ -959,6 +1134,81 @@ int ngsx_rule_fill(const ngsx_mesh *mesh, const double *lset_v, int dt, int orde
   if (mesh->dim == 2) k_rule_fill<2><<<nb, 256, 0, st>>>(*mesh, lset_v, dd->cut_table, dt, rv, nv, ri, ni, transform_if, emit_uncut, offs, pts3, wts);
   else k_rule_fill<3><<<nb, 256, 0, st>>>(*mesh, lset_v, dd->cut_table, dt, rv, nv, ri, ni, transform_if, emit_uncut, offs, pts3, wts);
   NGSX_LAUNCH_CHECK();
+  return NGSX_OK;
+}
+
+int ngsx_classify_integrate(const ngsx_mesh *mesh, const double *lset_v, uint32_t *cdom_words, int8_t *dom, double *ratio, int64_t *err,
+                            int32_t nint, const int32_t *h_dt, const int32_t *h_order, const ngsx_poly *h_f, double *out, void *stream) {
+  if (int rc = check_mesh(mesh)) return rc;
+  NGSX_REQUIRE(lset_v || mesh->ne == 0, "classify_integrate: lset_v is NULL");
+  NGSX_REQUIRE(nint >= 0 && nint <= FUSE_MAXINT && (nint == 0 || (h_dt && h_order && h_f && out)), "classify_integrate: bad integrals (at most 4)");
+  const DeviceData *dd = device_data();
+  if (!dd) return NGSX_ERR_CUDA;
+  cudaStream_t st = as_stream(stream);
+  if (err) { if (int rc = reset_err(err, st)) return rc; }
+  if (mesh->ne == 0) { if (nint) NGSX_CUDA(cudaMemsetAsync(out, 0, nint * sizeof(double), st)); return NGSX_OK; }
+  NGSX_REQUIRE(mesh->dim == 2 || (reinterpret_cast<uintptr_t>(mesh->el2v) & 15u) == 0, "classify_integrate: a 3D mesh.el2v must be 16-byte aligned");
+  const int64_t ne = mesh->ne, nwords = (ne + 31) / 32;
+  const int64_t nred = (int64_t)nblocks(ne, 256) * 8;                 // the reduction shape of ngsx_integrate
+  const unsigned nmid = (unsigned)std::min<int64_t>((nred + 255) / 256, 296);
+  FusedInt I{};
+  I.n = nint;
+  const double4 *ri[FUSE_MAXINT] = {nullptr, nullptr, nullptr, nullptr};
+  int ni[FUSE_MAXINT] = {0, 0, 0, 0};
+  double wref_if[FUSE_MAXINT] = {0.0, 0.0, 0.0, 0.0};
+  for (int j = 0; j < nint; j++) {
+    NGSX_REQUIRE(h_dt[j] >= 0 && h_dt[j] <= 2 && h_f[j].nterms >= 0 && h_f[j].nterms <= NGSX_POLY_MAXTERMS, "classify_integrate: bad integral");
+    if (int rc = lookup_rules(dd, mesh->dim, h_order[j], &I.rule_vol[j], &I.nr_vol[j], &ri[j], &ni[j])) return rc;
+    I.dt[j] = h_dt[j];
+    I.f[j].n = h_f[j].nterms;
+    for (int m = 0; m < I.f[j].n; m++) { I.f[j].c[m] = h_f[j].coef[m]; for (int d = 0; d < 3; d++) I.f[j].ex[m][d] = h_f[j].ex[m][d]; }
+    I.fconst[j] = I.f[j].n == 1 && I.f[j].ex[0][0] == 0 && I.f[j].ex[0][1] == 0 && I.f[j].ex[0][2] == 0;
+    I.wref_vol[j] = rule_weight_sum(mesh->dim, h_order[j]);
+    wref_if[j] = rule_weight_sum(mesh->dim - 1, h_order[j]);
+  }
+  double *partial = nullptr;
+  uint32_t *tmp = nullptr;
+  if (nint) NGSX_CUDA(cudaMallocAsync(&partial, (size_t)nint * (nred + nmid) * sizeof(double), st));
+  uint32_t *ifwords = cdom_words ? cdom_words + NGSX_CDOM_IF * nwords : nullptr;
+  if (!ifwords) { NGSX_CUDA(cudaMallocAsync(&tmp, nwords * sizeof(uint32_t), st)); ifwords = tmp; }
+  double *mid = partial ? partial + (size_t)nint * nred : nullptr;
+  for (int j = 0; j < nint; j++) I.partial[j] = partial + (size_t)j * nred;
+  const int64_t nchunks = (ne + STREAM_CH - 1) / STREAM_CH;
+  const unsigned nb = (unsigned)std::min<int64_t>(nchunks, (int64_t)dd->sm_count * 2);
+  const unsigned gcut = (unsigned)(((nwords + 31) / 32 + CUT_G - 1) / CUT_G);
+  auto *e = reinterpret_cast<unsigned long long *>(err);
+  cudaError_t e0 = cudaSuccess;
+  int launches = 1;
+  if (mesh->dim == 2) {
+    static const cudaError_t attr = cudaFuncSetAttribute(k_fused_sweep<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)stream_smem<2>());
+    e0 = attr;
+    k_fused_sweep<2><<<nb, STREAM_THREADS, stream_smem<2>(), st>>>(*mesh, lset_v, cdom_words, tmp, nwords, dom, ratio, e, I, nred);
+    if (ratio) { k_classify_cut<2><<<gcut, 256, 0, st>>>(*mesh, lset_v, dd->cut_table, ifwords, nwords, ratio); launches++; }
+    for (int j = 0; j < nint; j++)
+      launch_int_cut<2>(I.dt[j] == IF, I.fconst[j], gcut, st, *mesh, lset_v, dd->cut_table, I.dt[j], I.rule_vol[j], I.nr_vol[j], ri[j], ni[j], I.f[j],
+                        I.fconst[j], I.wref_vol[j], wref_if[j], (const uint32_t *)ifwords, nwords, I.partial[j]);
+  } else {
+    static const cudaError_t attr = cudaFuncSetAttribute(k_fused_sweep<3>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)stream_smem<3>());
+    e0 = attr;
+    k_fused_sweep<3><<<nb, STREAM_THREADS, stream_smem<3>(), st>>>(*mesh, lset_v, cdom_words, tmp, nwords, dom, ratio, e, I, nred);
+    if (ratio) { k_classify_cut<3><<<gcut, 256, 0, st>>>(*mesh, lset_v, dd->cut_table, ifwords, nwords, ratio); launches++; }
+    for (int j = 0; j < nint; j++)
+      launch_int_cut<3>(I.dt[j] == IF, I.fconst[j], gcut, st, *mesh, lset_v, dd->cut_table, I.dt[j], I.rule_vol[j], I.nr_vol[j], ri[j], ni[j], I.f[j],
+                        I.fconst[j], I.wref_vol[j], wref_if[j], (const uint32_t *)ifwords, nwords, I.partial[j]);
+  }
+  cudaError_t e1 = cudaGetLastError();
+  if (nint) {
+    k_int_reduce_multi<<<dim3(nmid, nint), 256, 0, st>>>(nred, nred, partial, mid, (int)nmid);
+    k_reduce_final_multi<<<nint, 1024, 0, st>>>(nmid, mid, out);
+    launches += nint + 2;
+  }
+  g_launches.fetch_add(launches);
+  cudaError_t e2 = cudaGetLastError();
+  if (partial) cudaFreeAsync(partial, st);
+  if (tmp) cudaFreeAsync(tmp, st);
+  NGSX_CUDA(e0);
+  NGSX_CUDA(e1);
+  NGSX_CUDA(e2);
   return NGSX_OK;
 }
 

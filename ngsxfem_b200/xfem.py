@@ -157,6 +157,25 @@ class CutInfo:
         return self.ratio if VOL_or_BND == VOL else self._boundary()[2]
 
 
+def UpdateAndIntegrate(cutinfo: CutInfo, levelset, integrals, sync: bool = False):
+    """CutInfo.Update(levelset) and Integrate(levelset_domain = {levelset, domain_type}, cf, order) for every (domain_type, order,
+    cf) of `integrals` (at most 4) in ONE pass over the element table (ngsx_classify_integrate): the same results, bit for bit,
+    as the separate calls.  Returns a device tensor with the integrals (a list of floats with sync = True)."""
+    mesh = cutinfo.mesh
+    if getattr(mesh, "tensor", False) or mesh.c_deformation() is not None:
+        raise NgsxError(-2, "UpdateAndIntegrate: affine simplex meshes only (use the separate calls)")
+    lv = _lset_vec(levelset)
+    n = len(integrals)
+    dts = (ctypes.c_int32 * max(n, 1))(*[int(t[0]) for t in integrals])
+    orders = (ctypes.c_int32 * max(n, 1))(*[int(t[1]) for t in integrals])
+    polys = (_lib.Poly * max(n, 1))(*[_poly_of(t[2] if len(t) > 2 else 1.0) for t in integrals])
+    out = torch.zeros(max(n, 1), dtype=torch.float64, device=mesh.device)
+    check(_lib_().ngsx_classify_integrate(ctypes.byref(mesh.c_struct()), _ptr(lv), _ptr(cutinfo.words), _ptr(cutinfo.dom), _ptr(cutinfo.ratio),
+                                          _ptr(cutinfo.err), n, dts, orders, polys, _ptr(out), _stream()))
+    cutinfo._bnd, cutinfo._bnd_lv = None, lv
+    return out[:n].tolist() if sync else out[:n]
+
+
 class _CDT(int):
     """COMBINED_DOMAIN_TYPE value"""
     def __new__(cls, v):

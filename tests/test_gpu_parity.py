@@ -1844,3 +1844,28 @@ def test_deformed_xfem_compound_operator(X, dim, fo, dord):
     got = sp.csr_matrix((first.cpu().numpy(), a.mat.colidx.cpu().numpy(), a.mat.rowptr.cpu().numpy()), shape=ref.shape)
     assert abs(got - ref).max() <= 1e-11 * abs(ref).max()
     assert np.abs(fv.cpu().numpy() - rhs).max() <= 1e-12 * np.abs(rhs).max()
+
+
+@pytest.mark.parametrize("dim,nx", [(2, 70), (3, 21)])
+def test_fused_sweep_equals_separate_calls(X, dim, nx):
+    """ngsx_classify_integrate: CutInfo.Update + several Integrate calls in one pass over the element table -- bit arrays, domains,
+    cut ratios and every integral are bitwise those of the separate calls (same partial sums, same reduction tree)"""
+    xf, ngs = X.xfem, X.ngs
+    m = X.meshes.MakeStructured2DMesh(nx) if dim == 2 else X.meshes.MakeStructured3DMesh(nx)
+    mesh = ngs.Mesh(m)
+    gf = ngs.GridFunction(ngs.H1(mesh, order=1))
+    xf.InterpolateToP1(ngs.SphereLevelset((0.5,) * dim, 0.35), gf)
+    ci = xf.CutInfo(mesh, gf)
+    cf = 1.0 + ngs.x * ngs.y
+    want = [xf.IntegrateX(gf, mesh, cf=1.0, order=4, domain_type=IF, sync=False),
+            xf.IntegrateX(gf, mesh, cf=1.0, order=4, domain_type=NEG, sync=False),
+            xf.IntegrateX(gf, mesh, cf=cf, order=2, domain_type=POS, sync=False),
+            xf.IntegrateX(gf, mesh, cf=cf, order=3, domain_type=IF, sync=False)]
+    cj = xf.CutInfo(mesh)
+    got = xf.UpdateAndIntegrate(cj, gf, [(IF, 4, 1.0), (NEG, 4, 1.0), (POS, 2, cf), (IF, 3, cf)])
+    assert torch.equal(got, torch.cat(want))
+    assert torch.equal(cj.words, ci.words) and torch.equal(cj.dom, ci.dom)
+    assert torch.equal(cj.ratio, ci.ratio) and torch.equal(cj.err, ci.err)
+    one = xf.UpdateAndIntegrate(cj, gf, [(NEG, 4)], sync=True)
+    assert one == [float(want[1].item())]
+    assert xf.UpdateAndIntegrate(cj, gf, [], sync=True) == [] and torch.equal(cj.dom, ci.dom)
