@@ -1292,7 +1292,7 @@ def test_interpolate_p1_clamp_band(X):
     ci.check_degenerate()
     # without the clamp the same level set is one the reference throws on
     out3 = X.ngs.GridFunction(V1)
-    X.xfem.InterpolateToP1(X.ngs.x - 0.5, out3, eps_perturbation=0.0)
+    X.xfem.InterpolateToP1(X.ngs.x + X.ngs.y - 0.75, out3, eps_perturbation=0.0)     # zero at vertices of elements with both signs
     with pytest.raises(X.lib.NgsxError):
         X.xfem.CutInfo(mesh, out3).check_degenerate()
 

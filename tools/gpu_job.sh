@@ -5,7 +5,7 @@ TAG="${1:-job}"; MODE="${2:-full}"
 O=gpurun_out
 mkdir -p $O
 python __graft_entry__.py > $O/${TAG}_build.log 2>&1 || { tail -20 $O/${TAG}_build.log; exit 1; }
-timeout 1200 python -m pytest tests -q -m gpu -x > $O/${TAG}_tests.log 2>&1; echo "tests rc=$?"; tail -n 6 $O/${TAG}_tests.log
+timeout 1200 python -m pytest tests -q -m gpu --maxfail=12 > $O/${TAG}_tests.log 2>&1; echo "tests rc=$?"; grep -E "^(FAILED|ERROR)|passed|failed" $O/${TAG}_tests.log | tail -n 16
 python bench.py --steps 20 --warmup 5 > $O/${TAG}_bench.json 2> $O/${TAG}_bench.err; echo "bench rc=$?"; tail -c 300 $O/${TAG}_bench.err
 python - <<PY
 import json
