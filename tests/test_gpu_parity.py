@@ -1396,7 +1396,8 @@ def test_packed_rows_equal_dense_blocks(X, dim, fo):
         assert torch.equal(vals, a.mat.vals)
         # accumulate: twice the operator
         X.lib.check(L.ngsx_assemble_csr_rows_mats(plan.handle, mats.data_ptr(), 1, vals.data_ptr(), st))
-        assert torch.equal(vals, 2 * a.mat.vals)
+        # (v + r1) + r2 + ... is not bitwise 2 (r1 + r2 + ...)
+        assert torch.allclose(vals, 2 * a.mat.vals, rtol=1e-13, atol=1e-15 * float(a.mat.vals.abs().max()))
     mesh.UnsetDeformation()
 
 
@@ -1482,7 +1483,11 @@ def test_quad_hex_rules_against_reference_golden(X, name, dim):
     assert np.array_equal(ci.dom.cpu().numpy(), want)
     assert np.array_equal(ci.GetElementsOfType(X.xfem.HASNEG).to_bool().cpu().numpy(), want != POS)
     r = ci.ratio.cpu().numpy()
-    assert ((r[want == IF] > 0) & (r[want == IF] < 1)).all() and (r[want == NEG] == 1).all() and (r[want == POS] == 0).all()
+    assert (r[want == NEG] == 1).all() and (r[want == POS] == 0).all()
+    gn, go, _, gw = _golden_split(g, f"{name}_dt{NEG}_o1")                    # unit cells: the ratio is the NEG rule's weight sum
+    negvol = np.array([gw[go[k]:go[k + 1]].sum() for k in range(n)])
+    assert np.abs(r - negvol)[want == IF].max() <= 1e-12
+    assert ((r[want == IF] >= 0) & (r[want == IF] <= 1)).all()              # |lset| = 1e-14 slivers round to 0 / 1
 
 
 def test_quad_hex_reference_kats(X):
