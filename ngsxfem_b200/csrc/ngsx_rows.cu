@@ -208,9 +208,11 @@ struct RowArgs {
   const double *G;
   const double *cutmats;
   double *vals;
+  unsigned *counter;       // tile claim counter, zeroed before the launch
   int accumulate;
   // rule constants of the closed forms (row_vertex / row_edge)
   double m0, m2s, m2d, hm1, q3aab, q3abc, qm2d, qdm, q4[3];
+  double q3d, q4a, q4b;    // mask forms: q3aab - q3abc; q4(cnt) = q4[0] + cnt (q4a + q4b cnt), cnt = shared vertices of two edges
 };
 
 template <int J> __device__ __forceinline__ int desc_pos(const uint4 &d) {
@@ -258,32 +260,46 @@ __device__ __forceinline__ void row_vertex(const RowArgs &A, int i, const double
   }
 }
 
+// vertices of edge e from packed 2-bit tables (edge_vertices<DIM> for a run-time e without a select chain)
+template <int DIM> __device__ __forceinline__ void edge_vertices_rt(int e, int &a, int &b) {
+  constexpr uint32_t TA = DIM == 2 ? 0x6u : 0x43fu, TB = DIM == 2 ? 0x18u : 0xa64u;
+  a = (int)((TA >> (2 * e)) & 3u);
+  b = (int)((TB >> (2 * e)) & 3u);
+}
+
+// Edge row (a, b).  a and b are run-time values (the local row of the pair), the columns are compile-time: instead of
+// selecting K entries by comparing indices (two FSEL per double select, ~55 of them), the Kronecker deltas are 0.0 / 1.0
+// masks fa[c] = [c == a], fb[c] = [c == b] and the selects become fused multiply-adds on the otherwise idle FP64 pipe:
+//   corr(c, d) = fa[c] kb[d] + fa[d] kb[c] + fb[c] ka[d] + fb[d] ka[c]         (the M2(x, y) = m2d + (m2s - m2d) [x == y] part)
+//   M3, M4 terms: polynomials in fin[c] = fa[c] + fb[c] (0 / 1) and cnt = fin[c] + fin[d] (0 / 1 / 2), exact at those values
+//   up to one rounding of the host-computed coefficients.
 template <int DIM>
 __device__ __forceinline__ void row_edge(const RowArgs &A, int a, int b, const double *ga, const double *gb, double *v) {
   constexpr int NEDGE = H1<DIM, 2>::NEDGE;
-  double ka[DIM + 1], kb[DIM + 1], ks[DIM + 1];
+  double ka[DIM + 1], kb[DIM + 1], ks[DIM + 1], fa[DIM + 1], fb[DIM + 1], fin[DIM + 1];
   double sa = 0.0, sb = 0.0;
 #pragma unroll
   for (int c = 0; c < DIM; c++) { ka[c] = ga[c]; kb[c] = gb[c]; sa += ga[c]; sb += gb[c]; }
   ka[DIM] = -sa; kb[DIM] = -sb;
 #pragma unroll
-  for (int c = 0; c <= DIM; c++) ks[c] = ka[c] + kb[c];
+  for (int c = 0; c <= DIM; c++) {
+    ks[c] = ka[c] + kb[c];
+    fa[c] = __hiloint2double(c == a ? 0x3ff00000 : 0, 0);
+    fb[c] = __hiloint2double(c == b ? 0x3ff00000 : 0, 0);
+    fin[c] = fa[c] + fb[c];
+  }
   const double gm = ga[3];
-  const double gin = gm * A.q3aab, gout = gm * A.q3abc;
+  const double gd3 = gm * A.q3d, gout = gm * A.q3abc;
 #pragma unroll
-  for (int c = 0; c <= DIM; c++) v[c] = fma(A.hm1, ks[c], (c == a || c == b) ? gin : gout);
-  const double g0 = gm * A.q4[0], g1 = gm * A.q4[1], g2 = gm * A.q4[2];
+  for (int c = 0; c <= DIM; c++) v[c] = fma(A.hm1, ks[c], fma(fin[c], gd3, gout));
+  const double g0 = gm * A.q4[0], g4a = gm * A.q4a, g4b = gm * A.q4b;
 #pragma unroll
   for (int e = 0; e < NEDGE; e++) {
     int c, d;
     edge_vertices<DIM>(e, c, d);
-    double corr = 0.0;
-    if (a == c) corr += kb[d];
-    if (a == d) corr += kb[c];
-    if (b == c) corr += ka[d];
-    if (b == d) corr += ka[c];
-    const int cnt = (a == c) + (a == d) + (b == c) + (b == d);
-    const double gq = cnt == 2 ? g2 : (cnt == 1 ? g1 : g0);
+    const double corr = fma(fa[c], kb[d], fma(fa[d], kb[c], fma(fb[c], ka[d], fb[d] * ka[c])));
+    const double cnt = fin[c] + fin[d];
+    const double gq = fma(cnt, fma(cnt, g4b, g4a), g0);
     v[DIM + 1 + e] = fma(A.qm2d, ks[c] + ks[d], fma(A.qdm, corr, gq));
   }
 }
@@ -303,112 +319,196 @@ __device__ __forceinline__ void row_values_cut(const double *cm, double *v) {
   }
 }
 
-// the 128-byte line of a pair's geometry record(s) into L1, two steps before load_geo reads it
-template <int DIM>
-__device__ __forceinline__ void prefetch_geo(const RowArgs &A, uint32_t w0) {
-  prefetch_l1(A.G + (int64_t)(w0 & DESC_KMASK) * ((DIM + 1) * 4));
+// x * x the optimiser cannot see through (it knows bit 1 of a square is clear)
+__device__ __forceinline__ uint32_t opaque_square(uint32_t x) {
+  uint32_t y;
+  asm volatile("mul.lo.u32 %0, %1, %1;" : "=r"(y) : "r"(x));
+  return y;
 }
 
-// geometry record(s) of a pair: vertex row i -> record i; edge row (a, b) -> records a and b (the same 128-byte line)
+// geometry record(s) of a pair: vertex row i -> record i; edge row (a, b) -> records a and b (the same 128-byte line).
+// Returns 0 -- computed from the high bits of the record address, which the compiler cannot fold: added to the index of the
+// descriptor load that follows, it keeps that load BEHIND the address arithmetic here.  (Hoisted above it, the arithmetic
+// reuses registers of earlier loads and its scoreboard wait then also waits for the descriptor load just issued.)
 template <int DIM, int ORDER>
-__device__ __forceinline__ void load_geo(const RowArgs &A, uint32_t w0, double *ga, double *gb) {
+__device__ __forceinline__ uint32_t load_geo(const RowArgs &A, uint32_t w0, double *ga, double *gb) {
   constexpr int GS = (DIM + 1) * 4;
   const int i = (int)(w0 >> DESC_KBITS);
   const double *Gk = A.G + (int64_t)(w0 & DESC_KMASK) * GS;
+  int a = i, b = i;
+  if (ORDER == 2 && i > DIM) edge_vertices_rt<DIM>(i - (DIM + 1), a, b);
+  const double *pa = Gk + 4 * a;
+  ldg256(pa, ga);
+  if (ORDER == 2 && i > DIM) ldg256(Gk + 4 * b, gb);
+  return (uint32_t)(reinterpret_cast<uintptr_t>(pa) >> 60);
+}
+
+// Row of a quadrature (cut) element: nd doubles of the cut buffer added to the window.  Out of line on purpose -- inlined, its
+// loads take the scoreboard of the next step's descriptor / geometry loads and every step of the fast path waits for those.
+template <int ND>
+__device__ __noinline__ void cut_row_add(const double *__restrict__ cm, double *accrow, uint4 d) {
+  double v[ND];
+  int pos[ND];
+  row_values_cut<ND>(cm, v);
+  desc_positions<ND, 0>(d, pos);
+#pragma unroll
+  for (int j = 0; j < ND; j++) accrow[pos[j]] += v[j];
+}
+
+// one (row, element) pair with a constant rule: closed-form row added at the pair's column positions of the window
+template <int DIM, int ORDER>
+__device__ __forceinline__ void row_step(const RowArgs &A, double *accrow, const uint4 &d, const double *ga, const double *gb) {
+  constexpr int ND = H1<DIM, ORDER>::ND;
+  const int i = (int)(d.x >> DESC_KBITS);
+  double v[ND];
   if (ORDER == 1 || i <= DIM) {
-    ldg256(Gk + 4 * i, ga);
+    row_vertex<DIM, ORDER>(A, i, ga, v);
   } else {
-    int a, b;
-    edge_vertices<DIM>(i - (DIM + 1), a, b);
-    ldg256(Gk + 4 * a, ga);
-    ldg256(Gk + 4 * b, gb);
+    if constexpr (ORDER == 2) {
+      int ea, eb;
+      edge_vertices_rt<DIM>(i - (DIM + 1), ea, eb);
+      row_edge<DIM>(A, ea, eb, ga, gb, v);
+    }
   }
+  int pos[ND];
+  desc_positions<ND, 0>(d, pos);
+  // the nd columns of an element are distinct: read a batch, add, write it (no serialised read-modify-write chain; two
+  // batches keep the live registers under the 128 of four CTAs per SM)
+  constexpr int HB = (ND + 1) / 2;
+  double w[HB];
+#pragma unroll
+  for (int j = 0; j < HB; j++) w[j] = accrow[pos[j]];
+#pragma unroll
+  for (int j = 0; j < HB; j++) accrow[pos[j]] = w[j] + v[j];
+#pragma unroll
+  for (int j = HB; j < ND; j++) w[j - HB] = accrow[pos[j]];
+#pragma unroll
+  for (int j = HB; j < ND; j++) accrow[pos[j]] = w[j - HB] + v[j];
+}
+
+// 64-byte tile header global -> the warp's shared slot, asynchronously (lanes 0..3 move 16 bytes each)
+__device__ __forceinline__ void header_fetch(const TileHdr *src, TileHdr *slot, int lane) {
+  if (lane < 4) {
+    const uint32_t dst = (uint32_t)__cvta_generic_to_shared(reinterpret_cast<char *>(slot) + 16 * lane);
+    asm volatile("cp.async.ca.shared.global [%0], [%1], 16;" ::"r"(dst), "l"(reinterpret_cast<const char *>(src) + 16 * lane));
+  }
+  asm volatile("cp.async.commit_group;");
+}
+__device__ __forceinline__ void header_wait() {
+  asm volatile("cp.async.wait_all;" ::: "memory");
+  __syncwarp();
 }
 
 // WARP = one tile of consecutive CSR rows whose values (<= ACCW doubles) live in the warp's private shared-memory window:
 // initialised by the warp (zero, or the current values when accumulating), gathered, and streamed out once with coalesced
-// stores.  Warps never wait for each other.  LANE = the rows the schedule dealt to it: per step one (row, element) pair --
-// descriptor (the tile's block prefetched into L2 at tile start, registers three steps ahead, coalesced), geometry record(s)
-// (L1 prefetch two steps ahead, registers one step ahead), closed-form row, nd window adds.
+// stores.  Warps never wait for each other; they claim tiles from a counter in plan order (neighbouring tiles run at about
+// the same time: shared geometry records are L2 hits; no tail), one tile ahead so that the next header is in shared memory
+// and the first descriptors of the next tile fly while the window of this one is written out.
+// LANE = the rows the schedule dealt to it: per step one (row, element) pair.
+// Software pipeline in registers: at the top of step s the geometry of step s and the descriptors of steps s, s+1, s+2 have
+// landed; the geometry of step s+1 and the descriptor of step s+3 are issued there, and nothing else in the step reads or
+// writes their registers.  All global loads share one hardware scoreboard (a counter), so ANY wait on it after that point --
+// a register copy, an address computed into a register an earlier load wrote -- waits for the loads just issued as well.
+// Hence: the register rotation and the first read of this step's geometry sit at the very top (kept there by a data
+// dependence the optimiser cannot fold), the descriptor load is pinned behind the geometry address arithmetic, the
+// quadrature rows are out of line and last in the step (prefetched into L1 at the top), and two steps per trip let the two
+// geometry sets alternate without copies.
 // No two lanes share a row and the nd columns of one element are distinct, so every CSR entry is summed in plan order.
+#define NGSX_ROW_STEP(S, GA, GB, NA, NB)                                                   \
+  {                                                                                        \
+    const uint32_t ghi = (uint32_t)__double2hiint(GA[3]);                                  \
+    uint32_t zero = opaque_square(ghi | d2.x) & 2u;  /* squares are 0 or 1 mod 4 */        \
+    const uint4 d = d0;                                                                    \
+    d0 = d1; d1 = d2;                                                                      \
+    if ((S) + 1 < myload) zero = load_geo<DIM, ORDER>(A, d0.x + zero, NA, NB);             \
+    ldg128_if((S) + 3 < myload, A.desc + base3 + lane + zero, d2);                         \
+    base3 += __popc(__ballot_sync(0xffffffffu, (S) + 3 < myload));                         \
+    if ((S) < myload) {                                                                    \
+      double *accrow = acc + (d.y & 0xffffu);                                              \
+      const bool coded = GA[3] != GA[3];                                /* NaN-boxed code */ \
+      const unsigned payload = (unsigned)((unsigned long long)__double_as_longlong(GA[3]) & 0xffffffffULL); \
+      const bool cut = coded && payload != 0u;                                             \
+      const double *cm = A.cutmats + (int64_t)(payload - 1u) * NE + (int)(d.x >> DESC_KBITS) * ND; \
+      if (cut) { prefetch_l1(cm); prefetch_l1(cm + ND - 1); }         /* lands during the closed-form rows of the other lanes */ \
+      if (!coded) row_step<DIM, ORDER>(A, accrow, d, GA, GB);                              \
+      if (cut) cut_row_add<ND>(cm, accrow, d);                                             \
+    }                                                                                      \
+  }
+
+// descriptors of steps 0, 1, 2 of a tile
+#define NGSX_ROW_PRIME()                                                                   \
+  {                                                                                        \
+    d0 = null4; d1 = null4; d2 = null4;                                                    \
+    ldg128_if(0 < myload, A.desc + base3 + lane, d0);                                      \
+    base3 += __popc(__ballot_sync(0xffffffffu, 0 < myload));                               \
+    ldg128_if(1 < myload, A.desc + base3 + lane, d1);                                      \
+    base3 += __popc(__ballot_sync(0xffffffffu, 1 < myload));                               \
+    ldg128_if(2 < myload, A.desc + base3 + lane, d2);                                      \
+    base3 += __popc(__ballot_sync(0xffffffffu, 2 < myload));                               \
+  }
+
 template <int DIM, int ORDER>
 __global__ void __launch_bounds__(RW * 32, NGSX_MINBLOCKS) k_rows(RowArgs A) {
   constexpr int ND = H1<DIM, ORDER>::ND, NE = ND * ND;
   extern __shared__ __align__(16) double smem_rows[];
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   double *acc = smem_rows + warp * ACCW;
-  const int64_t nwarps = (int64_t)gridDim.x * RW;
+  TileHdr *slot = reinterpret_cast<TileHdr *>(smem_rows + RW * ACCW) + warp;
   const uint4 null4 = make_uint4(0xffffffffu, 0u, 0u, 0u);
-  for (int64_t tt = (int64_t)blockIdx.x * RW + warp; tt < A.ntiles; tt += nwarps) {
-    const TileHdr *H = A.tiles + tt;
-    const int64_t z0 = __ldg(&H->z0);
-    const int zlen = __ldg(&H->zlen), nsteps = __ldg(&H->nsteps);
-    const int myload = __ldg(&H->load[lane]);
-    int64_t base3 = __ldg(&H->d0);
-    prefetch_block_l2(A.desc, base3, __reduce_add_sync(0xffffffffu, myload), 16, lane);
-    if (tt + nwarps < A.ntiles) prefetch_l1(A.tiles + tt + nwarps);             // the next tile's header
-    // prime the pipeline: descriptors of steps 0, 1, 2, geometry of step 0 (registers) and of step 1 (L1)
-    uint4 dcur = null4, dnext = null4, dnext2 = null4;
-    if (0 < myload) dcur = __ldg(A.desc + base3 + lane);
-    base3 += __popc(__ballot_sync(0xffffffffu, 0 < myload));
-    if (1 < myload) dnext = __ldg(A.desc + base3 + lane);
-    base3 += __popc(__ballot_sync(0xffffffffu, 1 < myload));
-    if (2 < myload) dnext2 = __ldg(A.desc + base3 + lane);
-    base3 += __popc(__ballot_sync(0xffffffffu, 2 < myload));
-    double ga[4] = {0.0, 0.0, 0.0, 0.0}, gb[4] = {0.0, 0.0, 0.0, 0.0};
-    if (0 < myload) load_geo<DIM, ORDER>(A, dcur.x, ga, gb);
-    if (1 < myload) prefetch_geo<DIM>(A, dnext.x);
+  unsigned tt = 0;
+  if (lane == 0) tt = atomicAdd(A.counter, 1u);
+  tt = __shfl_sync(0xffffffffu, tt, 0);
+  if (tt >= A.ntiles) return;
+  header_fetch(A.tiles + tt, slot, lane);
+  header_wait();
+  int64_t z0 = slot->z0, base3 = slot->d0;
+  int zlen = slot->zlen, nsteps = slot->nsteps, myload = slot->load[lane];
+  uint4 d0, d1, d2;
+  NGSX_ROW_PRIME()
+  for (;;) {
+    __syncwarp();                                                  // every lane has read the slot
+    unsigned nxt = 0;
+    if (lane == 0) nxt = atomicAdd(A.counter, 1u);
+    nxt = __shfl_sync(0xffffffffu, nxt, 0);
+    const bool more = nxt < A.ntiles;
+    if (more) header_fetch(A.tiles + nxt, slot, lane);
     if (A.accumulate) for (int t = lane; t < zlen; t += 32) acc[t] = A.vals[z0 + t];
     else for (int t = lane; t < zlen; t += 32) acc[t] = 0.0;
+    double ga[4] = {0.0, 0.0, 0.0, 0.0}, gb[4] = {0.0, 0.0, 0.0, 0.0}, ha[4] = {0.0, 0.0, 0.0, 0.0}, hb[4] = {0.0, 0.0, 0.0, 0.0};
+    if (0 < myload) load_geo<DIM, ORDER>(A, d0.x, ga, gb);
     __syncwarp();
-    for (int s = 0; s < nsteps; s++) {
-      const uint4 d = dcur;
-      double a4[4], b4[4];
-#pragma unroll
-      for (int m = 0; m < 4; m++) { a4[m] = ga[m]; b4[m] = gb[m]; }
-      dcur = dnext; dnext = dnext2;
-      if (s + 3 < myload) dnext2 = __ldg(A.desc + base3 + lane);
-      base3 += __popc(__ballot_sync(0xffffffffu, s + 3 < myload));
-      if (s + 1 < myload) load_geo<DIM, ORDER>(A, dcur.x, ga, gb);
-      if (s + 2 < myload) prefetch_geo<DIM>(A, dnext.x);
-      if (s < myload) {
-        const int i = (int)(d.x >> DESC_KBITS);
-        const unsigned long long cb = (unsigned long long)__double_as_longlong(a4[3]);
-        const bool coded = a4[3] != a4[3];
-        const unsigned payload = (unsigned)(cb & 0xffffffffULL);
-        if (!coded || payload != 0u) {
-          double v[ND], w[ND];
-          int pos[ND];
-          desc_positions<ND, 0>(d, pos);
-          double *accrow = acc + (d.y & 0xffffu);
-          // the nd columns of an element are distinct: read all, add, write all (no serialised read-modify-write chain)
-#pragma unroll
-          for (int j = 0; j < ND; j++) w[j] = accrow[pos[j]];
-          if (coded) {
-            row_values_cut<ND>(A.cutmats + (int64_t)(payload - 1u) * NE + i * ND, v);
-          } else if (ORDER == 1 || i <= DIM) {
-            row_vertex<DIM, ORDER>(A, i, a4, v);
-          } else {
-            if constexpr (ORDER == 2) {
-              int ea, eb;
-              edge_vertices<DIM>(i - (DIM + 1), ea, eb);
-              row_edge<DIM>(A, ea, eb, a4, b4, v);
-            }
-          }
-#pragma unroll
-          for (int j = 0; j < ND; j++) accrow[pos[j]] = w[j] + v[j];
-        }
-      }
+#if NGSX_ROWS_UNROLL == 2
+    for (int s = 0; s < nsteps; s += 2) {
+      NGSX_ROW_STEP(s, ga, gb, ha, hb)
+      if (s + 1 >= nsteps) break;
+      NGSX_ROW_STEP(s + 1, ha, hb, ga, gb)
     }
+#else
+    for (int s = 0; s < nsteps; s++) {
+      NGSX_ROW_STEP(s, ga, gb, ha, hb)
+#pragma unroll
+      for (int m = 0; m < 4; m++) { ga[m] = ha[m]; gb[m] = hb[m]; }
+    }
+#endif
     __syncwarp();
-    for (int t = lane; t < zlen; t += 32) A.vals[z0 + t] = acc[t];
-    __syncwarp();
+    const int64_t zc = z0;
+    const int zl = zlen;
+    if (more) {                                                    // the next tile's first descriptors fly during the write-out
+      header_wait();
+      z0 = slot->z0; base3 = slot->d0;
+      zlen = slot->zlen; nsteps = slot->nsteps; myload = slot->load[lane];
+      NGSX_ROW_PRIME()
+    }
+    for (int t = lane; t < zl; t += 32) A.vals[zc + t] = acc[t];
+    if (!more) break;
   }
 }
+#undef NGSX_ROW_STEP
+#undef NGSX_ROW_PRIME
 
 template <int DIM, int ORDER>
 static int launch_rows_t(const RowArgs &A, int sm_count, cudaStream_t st) {
-  size_t smem = (size_t)RW * ACCW * sizeof(double);
+  size_t smem = (size_t)RW * (ACCW * sizeof(double) + sizeof(TileHdr));
   auto kern = k_rows<DIM, ORDER>;
   NGSX_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   int occ = 0;
@@ -416,6 +516,7 @@ static int launch_rows_t(const RowArgs &A, int sm_count, cudaStream_t st) {
   if (occ < 1) { set_error("row kernel does not fit on an SM"); return NGSX_ERR_CUDA; }
   int64_t need = (A.ntiles + RW - 1) / RW;
   unsigned grid = (unsigned)std::max<int64_t>(1, std::min<int64_t>(need, (int64_t)sm_count * occ));
+  NGSX_CUDA(cudaMemsetAsync(A.counter, 0, sizeof(unsigned), st));
   kern<<<grid, RW * 32, smem, st>>>(A);
   NGSX_LAUNCH_CHECK();
   return NGSX_OK;
@@ -435,6 +536,7 @@ int rows_scratch(ngsx_rowplan *P, int dim) {
   if (!P->G) { NGSX_CUDA(cudaMalloc(&P->G, std::max<int64_t>(1, P->nlist) * (dim + 1) * 4 * sizeof(double))); P->g_dim = dim; }
   if (!P->cutlist) NGSX_CUDA(cudaMalloc(&P->cutlist, std::max<int64_t>(1, P->nlist) * sizeof(int32_t)));
   if (!P->cutcount) NGSX_CUDA(cudaMalloc(&P->cutcount, sizeof(int32_t)));
+  if (!P->counter) NGSX_CUDA(cudaMalloc(&P->counter, sizeof(unsigned)));
   return NGSX_OK;
 }
 
@@ -443,10 +545,13 @@ int launch_rows(const ngsx_rowplan *P, int dim, const RuleMom &M, int accumulate
   if (P->ds != 16) { set_error("row gather: this plan was built for merged facet-patch dof lists (use ngsx_assemble_csr_rows_mats)"); return NGSX_ERR_ARG; }
   RowArgs A{};
   A.ntiles = P->ntiles; A.tiles = P->tiles; A.desc = reinterpret_cast<const uint4 *>(P->desc); A.G = P->G; A.cutmats = P->cutmats;
-  A.vals = vals; A.accumulate = accumulate;
+  A.vals = vals; A.accumulate = accumulate; A.counter = P->counter;
   A.m0 = M.m0; A.m2s = M.m2s; A.m2d = M.m2d; A.hm1 = -0.5 * M.m1; A.q3aab = -0.5 * M.m3aab; A.q3abc = -0.5 * M.m3abc;
   A.qm2d = 0.25 * M.m2d; A.qdm = 0.25 * (M.m2s - M.m2d);
   A.q4[0] = 0.25 * M.m4abcd; A.q4[1] = 0.25 * M.m4aabc; A.q4[2] = 0.25 * M.m4aabb;
+  A.q3d = A.q3aab - A.q3abc;
+  A.q4b = 0.5 * (A.q4[2] - 2.0 * A.q4[1] + A.q4[0]);
+  A.q4a = A.q4[1] - A.q4[0] - A.q4b;
   switch (dim * 100 + P->nd) {
     case 203: return launch_rows_t<2, 1>(A, sm_count, st);
     case 206: return launch_rows_t<2, 2>(A, sm_count, st);
@@ -467,7 +572,7 @@ int ngsx_rowplan_destroy(ngsx_rowplan *P) {
   if (!P) return NGSX_OK;
   cudaDeviceSynchronize();
   cudaFree(P->tiles); cudaFree(P->desc); cudaFree(P->rowslot);
-  cudaFree(P->G); cudaFree(P->cutlist); cudaFree(P->cutcount); cudaFree(P->cutmats);
+  cudaFree(P->G); cudaFree(P->cutlist); cudaFree(P->cutcount); cudaFree(P->cutmats); cudaFree(P->counter);
   delete P;
   return NGSX_OK;
 }

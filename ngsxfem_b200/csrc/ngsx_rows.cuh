@@ -45,6 +45,7 @@ struct ngsx_rowplan {
   double *G = nullptr;              // [nlist][dim+1][4] per local vertex a: K[a][0..dim-1], (pad), |det J| c_mass  -- or a NaN-boxed code
   int32_t *cutlist = nullptr;       // [nlist] list indices of the elements that need quadrature
   int32_t *cutcount = nullptr;      // [1] work-list length of the last call (may exceed cut_cap: the overflow is reported)
+  unsigned *counter = nullptr;      // [1] tile claim counter of the row kernels
   double *cutmats = nullptr;        // [cut_cap][nd*nd]
   int64_t cut_cap = 0;
   int g_dim = 0;
@@ -65,6 +66,9 @@ namespace ngsx {
 #ifndef NGSX_MINBLOCKS
 #define NGSX_MINBLOCKS 4
 #endif
+#ifndef NGSX_ROWS_UNROLL
+#define NGSX_ROWS_UNROLL 2
+#endif
 #ifndef NGSX_TILE_MAXPAIRS
 #define NGSX_TILE_MAXPAIRS 768
 #endif
@@ -81,6 +85,12 @@ constexpr unsigned long long GCODE_NAN = 0x7ff8000000000000ULL;
 // software prefetch (no destination register): the schedule is static, so a warp can pull the descriptor block of its tile into
 // L2 when it starts the tile, and the geometry record of a pair into L1 two steps before it is used
 __device__ __forceinline__ void prefetch_l2(const void *p) { asm volatile("prefetch.global.L2 [%0];" ::"l"(p)); }
+// predicated 128-bit load INTO d: the registers keep their value when p is false.  (An `if (p) d = __ldg(..)` may compile to a
+// load into a temporary and a predicated move right behind it, whose scoreboard wait exposes the full latency of the load.)
+__device__ __forceinline__ void ldg128_if(bool p, const void *ptr, uint4 &d) {
+  asm volatile("{\n\t.reg .pred q;\n\tsetp.ne.u32 q, %4, 0;\n\t@q ld.global.nc.v4.u32 {%0, %1, %2, %3}, [%5];\n\t}"
+               : "+r"(d.x), "+r"(d.y), "+r"(d.z), "+r"(d.w) : "r"((uint32_t)p), "l"(ptr));
+}
 __device__ __forceinline__ void prefetch_l1(const void *p) { asm volatile("prefetch.global.L1 [%0];" ::"l"(p)); }
 // the tile's contiguous block of `count` records of `bytes` bytes starting at record d0, 128-byte lines dealt to the lanes
 __device__ __forceinline__ void prefetch_block_l2(const void *base, int64_t d0, int count, int bytes, int lane) {

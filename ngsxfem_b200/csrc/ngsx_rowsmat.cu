@@ -31,6 +31,13 @@ struct RowMatArgs {
 template <int DS> struct Desc { uint4 w[DS / 16]; };
 
 template <int DS>
+__device__ __forceinline__ void ld_desc_if(bool p, const uint8_t *desc, int64_t slot, Desc<DS> &d) {
+  const uint4 *q = reinterpret_cast<const uint4 *>(desc + slot * DS);
+#pragma unroll
+  for (int t = 0; t < DS / 16; t++) ldg128_if(p, q + t, d.w[t]);
+}
+
+template <int DS>
 __device__ __forceinline__ Desc<DS> ld_desc(const uint8_t *desc, int64_t slot) {
   Desc<DS> d;
   const uint4 *q = reinterpret_cast<const uint4 *>(desc + slot * DS);
@@ -169,8 +176,8 @@ __global__ void __launch_bounds__(RW * 32) k_rows_packed(RowMatArgs A) {
     int cnt = __popc(__ballot_sync(0xffffffffu, 0 < myload));
     int64_t dbase = base + cnt;                                   // descriptor slot of (step 1, lane 0)
     {
-      if (0 < myload) d = ld_desc<DS>(A.desc, base + lane);
-      if (1 < myload) dn = ld_desc<DS>(A.desc, dbase + lane);
+      ld_desc_if<DS>(0 < myload, A.desc, base + lane, d);
+      ld_desc_if<DS>(1 < myload, A.desc, dbase + lane, dn);
       dbase += __popc(__ballot_sync(0xffffffffu, 1 < myload));
       const uint4 *src = reinterpret_cast<const uint4 *>(A.mats + base * NDP);
 #pragma unroll
@@ -187,7 +194,7 @@ __global__ void __launch_bounds__(RW * 32) k_rows_packed(RowMatArgs A) {
       base += cnt;
       cnt = __popc(__ballot_sync(0xffffffffu, s + 1 < myload));
       d = dn;
-      if (s + 2 < myload) dn = ld_desc<DS>(A.desc, dbase + lane);
+      ld_desc_if<DS>(s + 2 < myload, A.desc, dbase + lane, dn);
       dbase += __popc(__ballot_sync(0xffffffffu, s + 2 < myload));
       if (cnt > 0) {                                              // next step's run flies during the adds
         const uint4 *src = reinterpret_cast<const uint4 *>(A.mats + base * NDP);
