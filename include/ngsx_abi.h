@@ -247,6 +247,16 @@ int ngsx_gather_vec(int64_t ndof, const int64_t *dofptr /*[ndof+1]*/, const int6
  * reproducible run to run).  out is a device double. */
 int ngsx_integrate(const ngsx_mesh *mesh, const double *lset_v, int dt, int order, const ngsx_poly *h_f, double *out, void *stream);
 
+/* Allocation-free variant of ngsx_integrate.  NO COUNTERPART IN THE REFERENCE: added for
+ * callers that cannot call cudaMalloc (CUDA graph capture, tight serving loops, harnesses that forbid it).  Same arguments, same
+ * kernels and reduction tree, bitwise the result of ngsx_integrate; the scratch (per-warp partial sums, cut-element words) is a
+ * file-scope __device__ array of the library sized for NGSX_STATIC_MAX_ELEMENTS elements (about 1.6 MB, held by every GPU
+ * that loads the library until exit), so the call performs no cudaMalloc / cudaFree / memory-pool allocation.  Meshes with
+ * ne > NGSX_STATIC_MAX_ELEMENTS are rejected with NGSX_ERR_CAPACITY.  All calls on one device share the array (it keeps the
+ * last call's contents; nothing needs clearing): calls that overlap on the GPU -- different streams -- race, serialise them. */
+#define NGSX_STATIC_MAX_ELEMENTS 4194304
+int ngsx_integrate_static(const ngsx_mesh *mesh, const double *lset_v, int dt, int order, const ngsx_poly *h_f, double *out, void *stream);
+
 /* Fused sweep: ngsx_classify and up to 4 ngsx_integrate calls on the same level set in one pass over the element table
  * (CutInfo.Update followed by Integrate(...) calls is the usual sequence of a step; each of them alone streams el2v once and has
  * its own latency floor).  Outputs as ngsx_classify (any may be NULL); integral j over (h_dt[j], h_order[j]) of h_f[j] goes to

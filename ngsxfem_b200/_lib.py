@@ -99,6 +99,7 @@ SIGNATURES = {
                                           c_void_p, c_int, c_void_p, c_void_p, c_void_p]),
     "ngsx_set_gather_wait_event": (None, [c_void_p]),
     "ngsx_integrate": (c_int, [ctypes.POINTER(Mesh), c_void_p, c_int, c_int, ctypes.POINTER(Poly), c_void_p, c_void_p]),
+    "ngsx_integrate_static": (c_int, [ctypes.POINTER(Mesh), c_void_p, c_int, c_int, ctypes.POINTER(Poly), c_void_p, c_void_p]),
     "ngsx_elmat_h1_deformed": (c_int, [ctypes.POINTER(Mesh), ctypes.POINTER(Deformation), c_void_p, c_int, c_int, c_int, ctypes.POINTER(FormH1),
                                        c_i64, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p]),
     "ngsx_elvec_h1_deformed": (c_int, [ctypes.POINTER(Mesh), ctypes.POINTER(Deformation), c_void_p, c_int, c_int, c_int, ctypes.POINTER(Poly),

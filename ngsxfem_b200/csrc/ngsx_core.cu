@@ -979,6 +979,79 @@ using namespace ngsx;
 
 static inline unsigned nblocks(int64_t n, int bs) { return (unsigned)((n + bs - 1) / bs); }
 
+// ---- ngsx_integrate_static: the allocation-free variant of ngsx_integrate -----------------------------------------------
+// Scratch (per-warp partial sums, second reduction level, cut-element words) and the constant tables live in file-scope
+// __device__ arrays: every GPU that loads the library holds them (about 1.6 MB) until exit.  In host code these names are
+// host-side stand-ins, NOT device addresses: the addresses come from cudaGetSymbolAddress, once per device (static_setup).
+constexpr int64_t STATIC_MAX_NE = NGSX_STATIC_MAX_ELEMENTS;
+constexpr int64_t STATIC_MAX_NRED = (STATIC_MAX_NE + 255) / 256 * 8;
+constexpr int64_t STATIC_NMID = 296;
+constexpr size_t STATIC_PARTIAL_BYTES = (size_t)(STATIC_MAX_NRED + STATIC_NMID) * sizeof(double);
+constexpr size_t STATIC_SCRATCH_BYTES = STATIC_PARTIAL_BYTES + (size_t)STATIC_MAX_NRED * sizeof(uint32_t);
+constexpr int STATIC_NRULES = 1 + NGSX_RULE_SEGM_NPTS + NGSX_RULE_TRIG_NPTS + NGSX_RULE_TET_NPTS;
+static __device__ __align__(256) unsigned char s_int_scratch[STATIC_SCRATCH_BYTES];
+static __device__ __align__(256) double4 s_int_rules[STATIC_NRULES];
+static __device__ __align__(256) CutTable s_int_cut_table;
+
+struct StaticData {
+  bool ready = false;
+  unsigned char *scratch = nullptr;
+  DeviceData dd;                 // rules / cut_table point into the __device__ arrays above
+};
+static std::mutex g_static_mutex;
+static StaticData g_static[64];
+static const int s_rule_base[4] = {0, 1, 1 + NGSX_RULE_SEGM_NPTS, 1 + NGSX_RULE_SEGM_NPTS + NGSX_RULE_TRIG_NPTS};
+
+// once per device, with that device current: symbol addresses, constant tables copied in, kernel attributes.  No allocation.
+static const StaticData *static_setup() {
+  int dev = 0;
+  if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) { set_error("cudaGetDevice failed"); return nullptr; }
+  std::lock_guard<std::mutex> lock(g_static_mutex);
+  StaticData &S = g_static[dev];
+  if (S.ready) return &S;
+  cudaError_t e = cudaGetSymbolAddress((void **)&S.scratch, s_int_scratch);
+  if (e == cudaSuccess) e = cudaGetSymbolAddress((void **)&S.dd.rules, s_int_rules);
+  if (e == cudaSuccess) e = cudaGetSymbolAddress((void **)&S.dd.cut_table, s_int_cut_table);
+  if (e != cudaSuccess) { set_error(std::string("integrate_static: cudaGetSymbolAddress: ") + cudaGetErrorString(e)); return nullptr; }
+  static double4 h_rules[STATIC_NRULES];                           // host staging, fixed size
+  static CutTable h_tab;
+  int n = 0;
+  h_rules[n++] = make_double4(0, 0, 0, 1.0);
+  auto push = [&](const double (*d)[4], int cnt) { for (int i = 0; i < cnt; i++) h_rules[n++] = make_double4(d[i][0], d[i][1], d[i][2], d[i][3]); };
+  push(NGSX_RULE_SEGM_DATA, NGSX_RULE_SEGM_NPTS);
+  push(NGSX_RULE_TRIG_DATA, NGSX_RULE_TRIG_NPTS);
+  push(NGSX_RULE_TET_DATA, NGSX_RULE_TET_NPTS);
+  for (int dim = 2; dim <= 3; dim++)
+    for (int dt = 0; dt < 3; dt++)
+      for (int mask = 0; mask < 16; mask++) build_cut_entry(dim, dt, mask, h_tab.e[dim - 2][dt][mask]);
+  e = cudaMemcpy(S.dd.rules, h_rules, sizeof(h_rules), cudaMemcpyHostToDevice);
+  if (e == cudaSuccess) e = cudaMemcpy(S.dd.cut_table, &h_tab, sizeof(CutTable), cudaMemcpyHostToDevice);
+  if (e == cudaSuccess) e = cudaDeviceGetAttribute(&S.dd.sm_count, cudaDevAttrMultiProcessorCount, dev);
+  if (e == cudaSuccess) e = cudaFuncSetAttribute(k_int_uncut<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)stream_smem<2>());
+  if (e == cudaSuccess) e = cudaFuncSetAttribute(k_int_uncut<3>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)stream_smem<3>());
+  if (e != cudaSuccess) { set_error(std::string("integrate_static set-up: ") + cudaGetErrorString(e)); return nullptr; }
+  S.ready = true;
+  return &S;
+}
+
+static bool static_rule_lookup(const StaticData *S, int sdim, int order, const double4 **ptr, int *n) {
+  if (order < 0) order = 0;
+  const int *offs = nullptr;
+  int maxo = 0;
+  switch (sdim) {
+    case 0: *ptr = S->dd.rules; *n = 1; return true;
+    case 1: offs = NGSX_RULE_SEGM_OFFS; maxo = NGSX_RULE_SEGM_MAXORDER; break;
+    case 2: offs = NGSX_RULE_TRIG_OFFS; maxo = NGSX_RULE_TRIG_MAXORDER; break;
+    case 3: offs = NGSX_RULE_TET_OFFS; maxo = NGSX_RULE_TET_MAXORDER; break;
+    default: return false;
+  }
+  if (order > maxo) return false;
+  *ptr = S->dd.rules + s_rule_base[sdim] + offs[order];
+  *n = offs[order + 1] - offs[order];
+  return true;
+}
+
+
 extern "C" {
 
 void ngsx_set_packed_output(const int32_t *d_rowslot) { ngsx::g_packed_output = d_rowslot; }
@@ -1299,6 +1372,60 @@ int ngsx_dofs_of_elements(int64_t n, int32_t nd, const int32_t *table, const uin
   if (n == 0) return NGSX_OK;
   k_dofs_of_elements<<<nblocks(n * nd, 256), 256, 0, st>>>(n, nd, table, a_words, out_words);
   NGSX_LAUNCH_CHECK();
+  return NGSX_OK;
+}
+
+// Allocation-free ngsx_integrate: same kernels, same launch shapes, same reduction tree (bitwise the same result); the scratch
+// is the static device array.  All calls on a device share it: calls that overlap on the GPU (different streams) race.  It
+// keeps the last call's contents; nothing has to start at zero -- k_int_uncut writes every partial and every cut word it or
+// the later kernels read.  No cudaMalloc / cudaFree / pool allocation on this path.
+int ngsx_integrate_static(const ngsx_mesh *mesh, const double *lset_v, int dt, int order, const ngsx_poly *h_f, double *out, void *stream) {
+  if (int rc = check_mesh(mesh)) return rc;
+  NGSX_REQUIRE(dt >= 0 && dt <= 2 && h_f && out && lset_v, "integrate_static: bad arguments");
+  NGSX_REQUIRE(h_f->nterms >= 0 && h_f->nterms <= NGSX_POLY_MAXTERMS, "integrate_static: too many polynomial terms");
+  if (mesh->ne > STATIC_MAX_NE) {
+    set_error("integrate_static: mesh.ne = " + std::to_string((long long)mesh->ne) + " exceeds NGSX_STATIC_MAX_ELEMENTS = " +
+              std::to_string((long long)STATIC_MAX_NE) + " (the static scratch array); use ngsx_integrate");
+    return NGSX_ERR_CAPACITY;
+  }
+  const StaticData *S = static_setup();
+  if (!S) return NGSX_ERR_CUDA;
+  const double4 *rv, *ri;
+  int nv, ni;
+  if (!static_rule_lookup(S, mesh->dim, order, &rv, &nv) || !static_rule_lookup(S, mesh->dim - 1, order, &ri, &ni)) {
+    set_error("integration order beyond the tabulated reference rules");
+    return NGSX_ERR_UNSUPPORTED;
+  }
+  cudaStream_t st = as_stream(stream);
+  if (mesh->ne == 0) { NGSX_CUDA(cudaMemsetAsync(out, 0, sizeof(double), st)); return NGSX_OK; }
+  NGSX_REQUIRE(mesh->dim == 2 || (reinterpret_cast<uintptr_t>(mesh->el2v) & 15u) == 0, "integrate_static: a 3D mesh.el2v must be 16-byte aligned");
+  PolyDev f;
+  f.n = h_f->nterms;
+  for (int m = 0; m < f.n; m++) { f.c[m] = h_f->coef[m]; for (int d = 0; d < 3; d++) f.ex[m][d] = h_f->ex[m][d]; }
+  const int fconst = f.n == 1 && f.ex[0][0] == 0 && f.ex[0][1] == 0 && f.ex[0][2] == 0;
+  const double wref_vol = rule_weight_sum(mesh->dim, order), wref_if = rule_weight_sum(mesh->dim - 1, order);
+  const int64_t ne = mesh->ne;
+  const int64_t nred = (int64_t)nblocks(ne, 256) * 8;
+  const unsigned nmid = (unsigned)std::min<int64_t>((nred + 255) / 256, STATIC_NMID);
+  double *partial = reinterpret_cast<double *>(S->scratch);                                  // [nred] + [nmid]
+  uint32_t *cutwords = reinterpret_cast<uint32_t *>(S->scratch + STATIC_PARTIAL_BYTES);      // [nred]
+  const int64_t nchunks = (ne + STREAM_CH - 1) / STREAM_CH;
+  const unsigned nb = (unsigned)std::min<int64_t>(nchunks, (int64_t)S->dd.sm_count * NGSX_INT_MINB);
+  const unsigned ncut = (unsigned)(((nred + 31) / 32 + CUT_G - 1) / CUT_G);
+  if (mesh->dim == 2) {
+    k_int_uncut<2><<<nb, STREAM_THREADS, stream_smem<2>(), st>>>(*mesh, lset_v, dt, rv, nv, f, fconst, wref_vol, partial, cutwords, nred);
+    launch_int_cut<2>(dt == IF, fconst, ncut, st, *mesh, lset_v, S->dd.cut_table, dt, rv, nv, ri, ni, f, fconst, wref_vol, wref_if, cutwords, nred, partial);
+  } else {
+    k_int_uncut<3><<<nb, STREAM_THREADS, stream_smem<3>(), st>>>(*mesh, lset_v, dt, rv, nv, f, fconst, wref_vol, partial, cutwords, nred);
+    launch_int_cut<3>(dt == IF, fconst, ncut, st, *mesh, lset_v, S->dd.cut_table, dt, rv, nv, ri, ni, f, fconst, wref_vol, wref_if, cutwords, nred, partial);
+  }
+  cudaError_t e1 = cudaGetLastError();
+  k_int_reduce<<<nmid, 256, 0, st>>>(nred, partial, partial + nred);
+  k_reduce_final<<<1, 1024, 0, st>>>(nmid, partial + nred, out);
+  g_launches.fetch_add(4);
+  cudaError_t e2 = cudaGetLastError();
+  NGSX_CUDA(e1);
+  NGSX_CUDA(e2);
   return NGSX_OK;
 }
 
