@@ -184,12 +184,39 @@ def run_b200(args):
     #   "after": the sweeps start when the whole chain is done;  "with": they start with the chain, the gather does not wait.
     order_default = os.environ.get("NGSX_BENCH_ORDER", "join")
 
+    # the three sweeps over the element table (CutInfo.Update, Integrate IF, Integrate NEG): "separate" = three calls (three
+    # streams), "fused" = xfem.UpdateAndIntegrate, one pass (ngsx_classify_integrate; bitwise the same results).  On 1/N of the
+    # mesh each sweep is at its latency floor.  Measured (B200): N = 1 fused 1.000 ms / separate 1.050 ms per step; one rank's share
+    # of an 8-GPU run (NGSX_BENCH_EMULATE=0/8) fused 0.220 / separate 0.204 -- there the three short sweeps run side by side on
+    # three streams and one pass over the rank's elements is the longer critical path.  Default: fused at N = 1, separate at N > 1.
+    sweep_mode = os.environ.get("NGSX_BENCH_SWEEPS", "fused" if pworld == 1 else "separate")
+    fused_list = [(xfem.IF, 4, 1.0), (xfem.NEG, 4, 1.0)]
+
     def step(record, serial=serial, timing=True, order=order_default):
         mk = ev if timing else (lambda: torch.cuda.Event())              # no timing events inside a graph capture
         e = [mk() for _ in range(6)]
         cur = torch.cuda.current_stream()
         e[0].record()
-        if serial:
+        if sweep_mode == "fused":
+            if serial:
+                r = xfem.UpdateAndIntegrate(ci, lsetp1, fused_list); e[1].record()
+                a.Assemble(); e[2].record(); e[3].record(); e[4].record()
+            else:
+                if order == "after":
+                    a.Assemble(); e[2].record()
+                    side[0].wait_event(e[2])
+                else:
+                    side[0].wait_event(e[0])
+                with torch.cuda.stream(side[0]):
+                    r = xfem.UpdateAndIntegrate(ci, lsetp1, fused_list); e[1].record(); e[3].record(); e[4].record()
+                if order == "join":
+                    a.Assemble(gather_after=e[4]); e[2].record()
+                elif order != "after":
+                    a.Assemble(); e[2].record()
+                cur.wait_stream(side[0])
+                r.record_stream(cur)
+            s_if, s_neg = r[0:1], r[1:2]
+        elif serial:
             ci.Update(lsetp1); e[1].record()
             a.Assemble(); e[2].record()
             s_if = xfem.IntegrateX(lsetp1, mesh_int, cf=1.0, order=4, domain_type=xfem.IF, sync=False); e[3].record()
@@ -253,7 +280,7 @@ def run_b200(args):
                 raise RuntimeError(f"graph replay differs from the eager step {chk} {int(wrote.sum())} {plan.nnz_covered}")
             a.mat.vals.copy_(ref_vals)
             del wrote
-            graph_note = f"CUDA graph per rank (assembly chain + three forked sweep streams, order '{order_default}'), NCCL all-reduce outside"
+            graph_note = f"CUDA graph per rank (assembly chain + three forked sweep streams, order '{order_default}', sweeps {sweep_mode}), NCCL all-reduce outside"
             del ref_vals
         except Exception as exc:                                         # capture unsupported on this driver: stay eager
             graph, graph_note = None, f"eager (graph capture failed: {type(exc).__name__}: {str(exc)[:200]})"
@@ -482,6 +509,8 @@ def run_b200(args):
                    "ne": mesh.ne, "hasneg_elements": n_global, "nnz": nnz_global, "assembly": a.assembly, "group": args.group, "colors": plan.ncolors,
                    "setup_s_untimed": round(setup_s, 2), "stage_ms": {"classify": cl_ms, "assemble": as_ms, "integrate": in_ms},
                    "stage_ms_one_stream": serial_break, "launch": graph_note,
+                   "sweeps": {"fused": "CutInfo.Update + Integrate(IF) + Integrate(NEG) in one pass over the element table (xfem.UpdateAndIntegrate / ngsx_classify_integrate, bitwise the separate calls); stage_ms.classify is that pass, stage_ms.integrate is 0",
+                              "separate": "three calls"}[sweep_mode],
                    "streams": "1 (serial stages)" if serial else {"join": "CutInfo.Update | Integrate(IF) | Integrate(NEG) on three streams beside k_geom + k_cutmat; the row gather waits for them (ngsx_set_gather_wait_event) and runs alone; stage_ms = step start to the stage's last kernel, 'assemble' therefore contains the wait",
                                                                      "after": "assemble, then CutInfo.Update | Integrate(IF) | Integrate(NEG) on three streams; stage_ms = stage start to its last kernel (the three sweeps overlap)",
                                                                      "with": "the three sweeps on three streams beside the whole assembly chain"}[order_default],

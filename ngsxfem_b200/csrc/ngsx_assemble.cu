@@ -644,6 +644,21 @@ __global__ void __launch_bounds__(256) k_geom(ngsx_mesh M, const double *__restr
 // goes to elmats[s].
 // ---------------------------------------------------------------------------------------------------------------
 constexpr int CUTMAT_THREADS = 128;
+// dynamic shared memory of the cut-element kernels: rules | decomposition table | per-warp staging of the output blocks
+__host__ __device__ inline size_t cutmat_stage_offset(int nr_vol, int nr_if) {
+  return ((size_t)(nr_vol + nr_if) * sizeof(double4) + 16 * sizeof(CutEntry) + 15) & ~(size_t)15;
+}
+// the staged blocks of `nvalid` consecutive work items -> their contiguous run in global memory, coalesced
+template <int NE, int ST>
+__device__ __forceinline__ void cutmat_flush(const double *stage, double *dst, int nvalid, int lane) {
+  __syncwarp();
+  const int total = nvalid * NE;
+  for (int t = lane; t < total; t += 32) {
+    const int el = t / NE, c = t - el * NE;
+    dst[t] = stage[el * ST + c];
+  }
+  __syncwarp();
+}
 
 template <int DIM, int ORDER, bool IFACE>
 __global__ void __launch_bounds__(CUTMAT_THREADS) k_cutmat(ElmatArgs A, int64_t count) {
@@ -658,7 +673,15 @@ __global__ void __launch_bounds__(CUTMAT_THREADS) k_cutmat(ElmatArgs A, int64_t 
   if (threadIdx.x < 16) lut[threadIdx.x] = A.tab->e[DIM - 2][A.dt][threadIdx.x];
   __syncthreads();
   if (A.d_count) count = min(count, (int64_t)*A.d_count);      // work list on the device, clamped to the caller's capacity
-  for (int64_t s = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; s < count; s += (int64_t)gridDim.x * blockDim.x) {
+  // the blocks of the 32 work items of a warp are one contiguous run of elmats: every lane writes its block into the warp's
+  // staging area (row stride odd: conflict-free) and the warp streams the run out with coalesced stores.  (Stored from the
+  // lanes directly, every store instruction touched 32 sectors in 32 lines and the kernel sat in the LSU queue.)
+  constexpr int ST = NE | 1;
+  const int lane = threadIdx.x & 31;
+  double *stage = reinterpret_cast<double *>(smem_raw + cutmat_stage_offset(A.nr_vol, A.nr_if)) + (size_t)(threadIdx.x >> 5) * 32 * ST;
+  for (int64_t s0 = (int64_t)blockIdx.x * blockDim.x + (threadIdx.x & ~31); s0 < count; s0 += (int64_t)gridDim.x * blockDim.x) {
+    const int64_t s = s0 + lane;
+    if (s < count) {
     const int64_t kk = A.sublist ? A.sublist[s] : s;
     const int64_t e = A.els ? A.els[kk] : kk;
     double ls[4], p[DIM + 1][DIM];
@@ -770,7 +793,7 @@ __global__ void __launch_bounds__(CUTMAT_THREADS) k_cutmat(ElmatArgs A, int64_t 
         }
       }
     }
-    double *out = A.elmats + s * NE;
+    double *out = stage + lane * ST;
     int t = 0;
 #pragma unroll
     for (int i = 0; i < ND; i++)
@@ -780,6 +803,8 @@ __global__ void __launch_bounds__(CUTMAT_THREADS) k_cutmat(ElmatArgs A, int64_t 
         if (j != i) out[j * ND + i] = acc[t];
         t++;
       }
+    }
+    cutmat_flush<NE, ST>(stage, A.elmats + s0 * NE, (int)min((int64_t)32, count - s0), lane);
   }
 }
 
@@ -807,7 +832,15 @@ __global__ void __launch_bounds__(CUTMAT_THREADS) k_cutmat_mom(ElmatArgs A, int6
   if (threadIdx.x < 16) lut[threadIdx.x] = A.tab->e[DIM - 2][A.dt][threadIdx.x];
   __syncthreads();
   if (A.d_count) count = min(count, (int64_t)*A.d_count);      // work list on the device, clamped to the caller's capacity
-  for (int64_t s = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; s < count; s += (int64_t)gridDim.x * blockDim.x) {
+  // the blocks of the 32 work items of a warp are one contiguous run of elmats: every lane writes its block into the warp's
+  // staging area (row stride odd: conflict-free) and the warp streams the run out with coalesced stores.  (Stored from the
+  // lanes directly, every store instruction touched 32 sectors in 32 lines and the kernel sat in the LSU queue.)
+  constexpr int ST = NE | 1;
+  const int lane = threadIdx.x & 31;
+  double *stage = reinterpret_cast<double *>(smem_raw + cutmat_stage_offset(A.nr_vol, A.nr_if)) + (size_t)(threadIdx.x >> 5) * 32 * ST;
+  for (int64_t s0 = (int64_t)blockIdx.x * blockDim.x + (threadIdx.x & ~31); s0 < count; s0 += (int64_t)gridDim.x * blockDim.x) {
+    const int64_t s = s0 + lane;
+    if (s < count) {
     const int64_t kk = A.sublist ? A.sublist[s] : s;
     const int64_t e = A.els ? A.els[kk] : kk;
     double ls[4], p[DIM + 1][DIM];
@@ -921,7 +954,7 @@ __global__ void __launch_bounds__(CUTMAT_THREADS) k_cutmat_mom(ElmatArgs A, int6
         for (int d = 0; d < DIM; d++) v = fma(gl[a][d], gl[b][d], v);
         gm[a * (a + 1) / 2 + b] = cs * v;
       }
-    double *out = A.elmats + s * NE;
+    double *out = stage + lane * ST;
 #pragma unroll
     for (int i = 0; i < NV; i++)
 #pragma unroll
@@ -959,6 +992,8 @@ __global__ void __launch_bounds__(CUTMAT_THREADS) k_cutmat_mom(ElmatArgs A, int6
         }
       }
     }
+    }
+    cutmat_flush<NE, ST>(stage, A.elmats + s0 * NE, (int)min((int64_t)32, count - s0), lane);
   }
 }
 
@@ -966,9 +1001,11 @@ static int g_use_fast = 1;
 
 template <int DIM, int ORDER, bool IFACE>
 static int launch_cutmat_t(const ElmatArgs &A, int sm_count, int64_t maxcount, cudaStream_t st) {
-  size_t smem = (size_t)(A.nr_vol + A.nr_if) * sizeof(double4) + 16 * sizeof(CutEntry);
+  constexpr int NE = H1<DIM, ORDER>::ND * H1<DIM, ORDER>::ND;
+  size_t smem = cutmat_stage_offset(A.nr_vol, A.nr_if) + (size_t)(CUTMAT_THREADS / 32) * 32 * (NE | 1) * sizeof(double);
   const bool mom = g_use_fast && A.form.cn == 0.0 && A.form.cd == 0.0;
   auto kern = mom ? k_cutmat_mom<DIM, ORDER, IFACE> : k_cutmat<DIM, ORDER, IFACE>;
+  NGSX_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   int occ = 0;
   NGSX_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, kern, CUTMAT_THREADS, smem));
   if (occ < 1) { set_error("cut-element kernel does not fit on an SM"); return NGSX_ERR_CUDA; }
