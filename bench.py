@@ -182,14 +182,15 @@ def run_b200(args):
     #   "join"  (default): the sweeps start with the chain, and the row gather waits for them (ngsx_set_gather_wait_event): the
     #            latency-bound sweeps share the machine with the small geometry / quadrature kernels, the gather runs alone;
     #   "after": the sweeps start when the whole chain is done;  "with": they start with the chain, the gather does not wait.
-    order_default = os.environ.get("NGSX_BENCH_ORDER", "join")
+    # Measured defaults: N = 1 "join" (1.000 ms; "with" 1.022, "after" 1.014); one rank's share of an N-GPU run "with" (the short
+    # gather does not wait for the sweep: 1/2 0.492 vs 0.518 ms "join", 1/4 0.277 vs 0.304, 1/8 0.172 vs 0.199).
+    order_default = os.environ.get("NGSX_BENCH_ORDER", "join" if pworld == 1 else "with")
 
     # the three sweeps over the element table (CutInfo.Update, Integrate IF, Integrate NEG): "separate" = three calls (three
     # streams), "fused" = xfem.UpdateAndIntegrate, one pass (ngsx_classify_integrate; bitwise the same results).  On 1/N of the
     # mesh each sweep is at its latency floor.  Measured (B200): N = 1 fused 1.000 ms / separate 1.050 ms per step; one rank's share
-    # of an 8-GPU run (NGSX_BENCH_EMULATE=0/8) fused 0.220 / separate 0.204 -- there the three short sweeps run side by side on
-    # three streams and one pass over the rank's elements is the longer critical path.  Default: fused at N = 1, separate at N > 1.
-    sweep_mode = os.environ.get("NGSX_BENCH_SWEEPS", "fused" if pworld == 1 else "separate")
+    # of an 8-GPU run (NGSX_BENCH_EMULATE=0/8), order "with": fused 0.172 / separate 0.191.
+    sweep_mode = os.environ.get("NGSX_BENCH_SWEEPS", "fused")
     fused_list = [(xfem.IF, 4, 1.0), (xfem.NEG, 4, 1.0)]
 
     def step(record, serial=serial, timing=True, order=order_default):

@@ -582,13 +582,21 @@ template <int DIM>
 __global__ void __launch_bounds__(256) k_geom(ngsx_mesh M, const double *__restrict__ lset, const int32_t *__restrict__ els, int64_t nlist,
                                              int dt, FormDev form, int use_fast, double *__restrict__ G, int32_t *__restrict__ cutlist,
                                              int32_t *__restrict__ cutcount, int64_t cut_cap, unsigned long long *__restrict__ err) {
-  int64_t k = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-  if (k >= nlist) return;
-  const int64_t e = els ? els[k] : k;
+  // the records of the 32 elements of a warp are one contiguous run of G: staged in shared memory (lane stride 144 bytes:
+  // conflict-free 128-bit stores) and written out with coalesced 256-bit stores
+  constexpr int NV = DIM + 1, LSTR = NV * 4 + 2;
+  __shared__ __align__(32) double sstage[8][32 * LSTR];
+  const int lane = threadIdx.x & 31;
+  double *stage = sstage[threadIdx.x >> 5];
+  const int64_t k = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  const int64_t k0 = k - lane;
+  if (k0 >= nlist) return;                                               // warp-uniform
+  const bool active = k < nlist;
+  const int64_t e = active ? (els ? els[k] : k) : 0;
   double ls[4], p[DIM + 1][DIM];
   load_el<DIM>(M, lset, e, ls, p);
   int mask;
-  const int dom = sign_test<DIM>(ls, mask);
+  const int dom = active ? sign_test<DIM>(ls, mask) : -2;
   double Kr[DIM + 1][3];
 #pragma unroll
   for (int a = 0; a <= DIM; a++) Kr[a][0] = Kr[a][1] = Kr[a][2] = 0.0;
@@ -631,9 +639,18 @@ __global__ void __launch_bounds__(256) k_geom(ngsx_mesh M, const double *__restr
       }
     }
   }
-  double4 *out = reinterpret_cast<double4 *>(G + k * ((DIM + 1) * 4));
+  double2 *mine = reinterpret_cast<double2 *>(stage + lane * LSTR);
 #pragma unroll
-  for (int a = 0; a <= DIM; a++) out[a] = make_double4(Kr[a][0], Kr[a][1], Kr[a][2], gm);
+  for (int a = 0; a <= DIM; a++) { mine[2 * a] = make_double2(Kr[a][0], Kr[a][1]); mine[2 * a + 1] = make_double2(Kr[a][2], gm); }
+  __syncwarp();
+  const int nrec = (int)min((int64_t)32, nlist - k0) * NV;               // 32-byte records of this warp's run
+  double *dst = G + k0 * (NV * 4);
+  for (int t = lane; t < nrec; t += 32) {
+    const int el = t / NV, a = t - el * NV;
+    const double2 *src = reinterpret_cast<const double2 *>(stage + el * LSTR + a * 4);
+    const double2 u = src[0], w = src[1];
+    asm volatile("st.global.v4.f64 [%0], {%1, %2, %3, %4};" ::"l"(dst + 4 * t), "d"(u.x), "d"(u.y), "d"(w.x), "d"(w.y) : "memory");
+  }
 }
 
 // ---------------------------------------------------------------------------------------------------------------

@@ -119,12 +119,16 @@ __global__ void __launch_bounds__(128) k_plan_desc(int64_t npairs, int64_t nrows
 
 // processing order of the tiles: by the list index of the first pair of the tile, so that the vertex-row and edge-row tiles of
 // one mesh region run at about the same time (their geometry records are then L2 hits)
+// Small plans (the geometry records of the whole list fit in L2: a rank's share of a multi-GPU run) are ordered by decreasing
+// step count instead, list index second: the warps claim tiles from a counter, so the longest tiles go first and the
+// kernel's tail is made of short ones (at 1/8 of config 2 the SMs finished between 113 K and 190 K cycles in mesh order).
 __global__ void __launch_bounds__(256) k_tile_keys(int64_t ntiles, const TileHdr *__restrict__ tiles, const uint8_t *__restrict__ desc, int ds,
-                                                  uint32_t *__restrict__ keys, int32_t *__restrict__ ids) {
+                                                  int by_cost, uint32_t *__restrict__ keys, int32_t *__restrict__ ids) {
   int64_t c = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (c >= ntiles) return;
   ids[c] = (int32_t)c;
-  keys[c] = *reinterpret_cast<const uint32_t *>(desc + tiles[c].d0 * ds) & DESC_KMASK;
+  const uint32_t k = *reinterpret_cast<const uint32_t *>(desc + tiles[c].d0 * ds) & DESC_KMASK;
+  keys[c] = by_cost ? ((uint32_t)(255 - min(tiles[c].nsteps, 255)) << 24) | (k >> 3) : k;
 }
 __global__ void __launch_bounds__(256) k_tile_permute(int64_t ntiles, const int32_t *__restrict__ order, const TileHdr *__restrict__ in,
                                                      TileHdr *__restrict__ out) {
@@ -809,7 +813,8 @@ static int rowplan_create(int64_t nlist, int32_t nd, const int32_t *table, int64
   PLAN_CUDA(cudaMalloc(&d_ck2, P->ntiles * sizeof(uint32_t)));
   PLAN_CUDA(cudaMalloc(&d_ids, P->ntiles * sizeof(int32_t)));
   PLAN_CUDA(cudaMalloc(&d_order, P->ntiles * sizeof(int32_t)));
-  k_tile_keys<<<(unsigned)((P->ntiles + 255) / 256), 256, 0, st>>>(P->ntiles, d_tiles_nat, P->desc, P->ds, d_ck, d_ids);
+  const int by_cost = nlist * 128 <= NGSX_ROWS_COSTORDER_BYTES;
+  k_tile_keys<<<(unsigned)((P->ntiles + 255) / 256), 256, 0, st>>>(P->ntiles, d_tiles_nat, P->desc, P->ds, by_cost, d_ck, d_ids);
   cudaFree(tmp); tmp = nullptr; tmp_bytes = 0;
   PLAN_CUDA(cub::DeviceRadixSort::SortPairs(nullptr, tmp_bytes, d_ck, d_ck2, d_ids, d_order, (int)P->ntiles, 0, 32, st));
   PLAN_CUDA(cudaMalloc(&tmp, tmp_bytes));

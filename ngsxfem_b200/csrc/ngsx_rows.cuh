@@ -69,6 +69,9 @@ namespace ngsx {
 #ifndef NGSX_ROWS_UNROLL
 #define NGSX_ROWS_UNROLL 2
 #endif
+#ifndef NGSX_ROWS_COSTORDER_BYTES
+#define NGSX_ROWS_COSTORDER_BYTES (64ll << 20)   // plans whose geometry records fit here: tiles ordered longest first
+#endif
 #ifndef NGSX_TILE_MAXPAIRS
 #define NGSX_TILE_MAXPAIRS 768
 #endif
