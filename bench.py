@@ -92,6 +92,29 @@ def measured_peak():
 
 
 # ======================================================================================================================
+def bind_to_gpu_numa_node(index):
+    """N > 1: run this rank (and first-touch its pinned staging buffers) on the cores of the NUMA node its GPU hangs off -- eight
+    ranks staging through one socket's memory share that socket's bandwidth.  Returns a note for the JSON line; never fails."""
+    try:
+        import torch
+        bus = torch.cuda.get_device_properties(index)
+        bdf = f"{bus.pci_domain_id:04x}:{bus.pci_bus_id:02x}:{bus.pci_device_id:02x}.0"
+        node = int(open(f"/sys/bus/pci/devices/{bdf}/numa_node").read())
+        if node < 0:
+            return f"gpu {bdf}: no NUMA node reported"
+        cpus = set()
+        for part in open(f"/sys/devices/system/node/node{node}/cpulist").read().strip().split(","):
+            a, _, b = part.partition("-")
+            cpus.update(range(int(a), int(b or a) + 1))
+        cpus &= os.sched_getaffinity(0)
+        if not cpus:
+            return f"gpu {bdf}: node {node} has no allowed cores"
+        os.sched_setaffinity(0, cpus)
+        return f"gpu {bdf}: node {node}, {len(cpus)} cores"
+    except Exception as exc:                                             # noqa: BLE001
+        return f"not bound ({type(exc).__name__}: {str(exc)[:80]})"
+
+
 def build_problem(nx, device, rank=0, world=1, group=6):
     import torch
     from ngsxfem_b200 import meshes, xfem
@@ -146,6 +169,7 @@ def run_b200(args):
     assert torch.cuda.is_available(), "bench.py needs a CUDA device: the CUDA library is the product, there is no CPU fallback"
     torch.cuda.set_device(lrank)
     dev = f"cuda:{lrank}"
+    numa_note = bind_to_gpu_numa_node(lrank) if world > 1 else None
     if world > 1:
         dist.init_process_group("nccl", device_id=torch.device(dev))
     import __graft_entry__ as ge
@@ -466,7 +490,12 @@ def run_b200(args):
                       statistics.mean(stage_ms["integrate"])], dtype=torch.float64, device=dev)
     owned_nnz = plan.nnz_covered if hasattr(plan, "nnz_covered") else a.mat.nnz
     cnt = torch.tensor([0, owned_nnz, launches], dtype=torch.int64, device=dev)
+    per_rank = None
     if world > 1:
+        allt = [torch.zeros_like(t) for _ in range(world)]
+        dist.all_gather(allt, t)
+        per_rank = {"ms_per_step": [round(float(x[0]) / args.steps, 5) for x in allt],
+                    "e2e_ms_per_step": [round(float(x[1]) / args.steps, 4) for x in allt]}
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         dist.all_reduce(cnt, op=dist.ReduceOp.SUM)
     total_ms, e2e_ms, cl_ms, as_ms, in_ms = t.tolist()
@@ -509,7 +538,7 @@ def run_b200(args):
         "config": {"workload": workload_name(args.nx, mesh.ne, n_global),
                    "ne": mesh.ne, "hasneg_elements": n_global, "nnz": nnz_global, "assembly": a.assembly, "group": args.group, "colors": plan.ncolors,
                    "setup_s_untimed": round(setup_s, 2), "stage_ms": {"classify": cl_ms, "assemble": as_ms, "integrate": in_ms},
-                   "stage_ms_one_stream": serial_break, "launch": graph_note,
+                   "stage_ms_one_stream": serial_break, "launch": graph_note, "per_rank": per_rank, "numa": numa_note,
                    "sweeps": {"fused": "CutInfo.Update + Integrate(IF) + Integrate(NEG) in one pass over the element table (xfem.UpdateAndIntegrate / ngsx_classify_integrate, bitwise the separate calls); stage_ms.classify is that pass, stage_ms.integrate is 0",
                               "separate": "three calls"}[sweep_mode],
                    "streams": "1 (serial stages)" if serial else {"join": "CutInfo.Update | Integrate(IF) | Integrate(NEG) on three streams beside k_geom + k_cutmat; the row gather waits for them (ngsx_set_gather_wait_event) and runs alone; stage_ms = step start to the stage's last kernel, 'assemble' therefore contains the wait",

@@ -1052,6 +1052,30 @@ static bool static_rule_lookup(const StaticData *S, int sdim, int order, const d
 }
 
 
+// Side streams of the fused sweep: its cut passes (cut ratios, one pass per integral) read the same bit array and write
+// disjoint outputs, so they run side by side behind the sweep -- forked from and joined back into the caller's stream with
+// events (legal under stream capture: the fork becomes parallel branches of the graph).  Created once per device.
+struct ForkPool {
+  bool ready = false;
+  cudaStream_t s[FUSE_MAXINT];
+  cudaEvent_t fork, join[FUSE_MAXINT];
+};
+static std::mutex g_fork_mutex, g_fork_enqueue_mutex;   // pool creation; one host thread at a time enqueues a fork / join
+static ForkPool g_fork[64];
+static ForkPool *fork_pool() {
+  int dev = 0;
+  if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) return nullptr;
+  std::lock_guard<std::mutex> lock(g_fork_mutex);
+  ForkPool &F = g_fork[dev];
+  if (F.ready) return &F;
+  if (cudaEventCreateWithFlags(&F.fork, cudaEventDisableTiming) != cudaSuccess) return nullptr;
+  for (int i = 0; i < FUSE_MAXINT; i++)
+    if (cudaStreamCreateWithFlags(&F.s[i], cudaStreamNonBlocking) != cudaSuccess ||
+        cudaEventCreateWithFlags(&F.join[i], cudaEventDisableTiming) != cudaSuccess) return nullptr;
+  F.ready = true;
+  return &F;
+}
+
 extern "C" {
 
 void ngsx_set_packed_output(const int32_t *d_rowslot) { ngsx::g_packed_output = d_rowslot; }
@@ -1252,24 +1276,44 @@ int ngsx_classify_integrate(const ngsx_mesh *mesh, const double *lset_v, uint32_
   auto *e = reinterpret_cast<unsigned long long *>(err);
   cudaError_t e0 = cudaSuccess;
   int launches = 1;
+  // the cut passes: the first on the caller's stream, the others on side streams forked behind the sweep
+  const int ntasks = (ratio ? 1 : 0) + nint;
+  ForkPool *F = ntasks > 1 ? fork_pool() : nullptr;
+  std::unique_lock<std::mutex> enqueue(g_fork_enqueue_mutex, std::defer_lock);
+  if (F) enqueue.lock();
+  int task = 0;
+  cudaError_t ef = cudaSuccess;
+  auto after_sweep = [&]() { if (F) ef = cudaEventRecord(F->fork, st); };
+  auto next_stream = [&]() -> cudaStream_t {
+    const int t = task++;
+    if (!F || t == 0) return st;
+    if (ef == cudaSuccess) ef = cudaStreamWaitEvent(F->s[t - 1], F->fork, 0);
+    return F->s[t - 1];
+  };
   if (mesh->dim == 2) {
     static const cudaError_t attr = cudaFuncSetAttribute(k_fused_sweep<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)stream_smem<2>());
     e0 = attr;
     k_fused_sweep<2><<<nb, STREAM_THREADS, stream_smem<2>(), st>>>(*mesh, lset_v, cdom_words, tmp, nwords, dom, ratio, e, I, nred);
-    if (ratio) { k_classify_cut<2><<<gcut, 256, 0, st>>>(*mesh, lset_v, dd->cut_table, ifwords, nwords, ratio); launches++; }
+    after_sweep();
+    if (ratio) { k_classify_cut<2><<<gcut, 256, 0, next_stream()>>>(*mesh, lset_v, dd->cut_table, ifwords, nwords, ratio); launches++; }
     for (int j = 0; j < nint; j++)
-      launch_int_cut<2>(I.dt[j] == IF, I.fconst[j], gcut, st, *mesh, lset_v, dd->cut_table, I.dt[j], I.rule_vol[j], I.nr_vol[j], ri[j], ni[j], I.f[j],
-                        I.fconst[j], I.wref_vol[j], wref_if[j], (const uint32_t *)ifwords, nwords, I.partial[j]);
+      launch_int_cut<2>(I.dt[j] == IF, I.fconst[j], gcut, next_stream(), *mesh, lset_v, dd->cut_table, I.dt[j], I.rule_vol[j], I.nr_vol[j], ri[j], ni[j],
+                        I.f[j], I.fconst[j], I.wref_vol[j], wref_if[j], (const uint32_t *)ifwords, nwords, I.partial[j]);
   } else {
     static const cudaError_t attr = cudaFuncSetAttribute(k_fused_sweep<3>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)stream_smem<3>());
     e0 = attr;
     k_fused_sweep<3><<<nb, STREAM_THREADS, stream_smem<3>(), st>>>(*mesh, lset_v, cdom_words, tmp, nwords, dom, ratio, e, I, nred);
-    if (ratio) { k_classify_cut<3><<<gcut, 256, 0, st>>>(*mesh, lset_v, dd->cut_table, ifwords, nwords, ratio); launches++; }
+    after_sweep();
+    if (ratio) { k_classify_cut<3><<<gcut, 256, 0, next_stream()>>>(*mesh, lset_v, dd->cut_table, ifwords, nwords, ratio); launches++; }
     for (int j = 0; j < nint; j++)
-      launch_int_cut<3>(I.dt[j] == IF, I.fconst[j], gcut, st, *mesh, lset_v, dd->cut_table, I.dt[j], I.rule_vol[j], I.nr_vol[j], ri[j], ni[j], I.f[j],
-                        I.fconst[j], I.wref_vol[j], wref_if[j], (const uint32_t *)ifwords, nwords, I.partial[j]);
+      launch_int_cut<3>(I.dt[j] == IF, I.fconst[j], gcut, next_stream(), *mesh, lset_v, dd->cut_table, I.dt[j], I.rule_vol[j], I.nr_vol[j], ri[j], ni[j],
+                        I.f[j], I.fconst[j], I.wref_vol[j], wref_if[j], (const uint32_t *)ifwords, nwords, I.partial[j]);
   }
   cudaError_t e1 = cudaGetLastError();
+  for (int t = 1; F && t < task; t++) {                                // join
+    if (ef == cudaSuccess) ef = cudaEventRecord(F->join[t - 1], F->s[t - 1]);
+    if (ef == cudaSuccess) ef = cudaStreamWaitEvent(st, F->join[t - 1], 0);
+  }
   if (nint) {
     k_int_reduce_multi<<<dim3(nmid, nint), 256, 0, st>>>(nred, nred, partial, mid, (int)nmid);
     k_reduce_final_multi<<<nint, 1024, 0, st>>>(nmid, mid, out);
@@ -1282,6 +1326,7 @@ int ngsx_classify_integrate(const ngsx_mesh *mesh, const double *lset_v, uint32_
   NGSX_CUDA(e0);
   NGSX_CUDA(e1);
   NGSX_CUDA(e2);
+  NGSX_CUDA(ef);
   return NGSX_OK;
 }
 
