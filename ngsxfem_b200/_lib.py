@@ -139,6 +139,8 @@ def load():
         fn.argtypes = args
     lib.ngsx_debug_set_fast_path.argtypes = [c_int]
     lib.ngsx_debug_set_fast_path.restype = None
+    lib.ngsx_debug_set_order3_fma.argtypes = [c_int]
+    lib.ngsx_debug_set_order3_fma.restype = None
     lib.ngsx_debug_set_deformed_warp.argtypes = [c_int]
     lib.ngsx_debug_set_deformed_warp.restype = None
     lib.ngsx_debug_set_timing.argtypes = [c_int]

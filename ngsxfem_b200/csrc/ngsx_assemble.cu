@@ -39,6 +39,7 @@ struct ElmatArgs {
   const int32_t *d_count;      // optional device-resident number of work items (overrides `count`)
   int group;                   // list entries per warp-sequential group
   int use_fast;                // constant-rule path for uncut elements
+  int32_t *work; int32_t *work_count;   // order 3, dense sink: pass 1 records the quadrature-path entries here, pass 2 walks them (output at the entry)
   // sinks
   double *elmats; int32_t *npts;          // dense
   const int32_t *slots; double *vals;     // CSR
@@ -331,6 +332,431 @@ __global__ void __launch_bounds__(WARPS * 32) k_elmat(ElmatArgs A, int64_t first
 }
 
 // ---------------------------------------------------------------------------------------------------------------
+// H1 order 3 element matrices (row g-1): warp per element, W3 warps per CTA.
+//  * uncut elements of the requested domain: constant-rule tables after all.  The only orientation dependence of the order-3
+//    basis is the SIGN of the second function of each edge (x = +-(lam_b - lam_a), NGS/fem/h1hofe_impl.hpp:78-108), so the block
+//    is  S T(J) S  with S = diag(+-1) and T the table contraction of the orientation-free element: 7 FMAs per entry instead of
+//    24 points x 4, no staging, one coalesced store of the block.
+//  * cut elements (and IF / Nitsche forms): the quadrature contraction  sum_q f_q b_i(q)^T Q b_j(q),  b = (phi, grad phi) in R^4,
+//    Q the 4x4 symmetric matrix of the form ([[c_m, c_n n^T],[c_n n, c_s I + c_d n n^T]]), runs on the FP64 tensor cores:
+//    per staged point ONE k-step of mma.sync.m8n8k4.f64 (DMMA.884) for each lower 8x8 tile of the block padded to 24 x 24
+//    (6 tiles; 3 for a P3 triangle).  A fragment = component lane%4 of b_{8r + lane/4}, B fragment = f_q (Q b_{8c + lane/4})[lane%4],
+//    both from one 32-byte row read (4 lanes share a row: broadcast, no bank conflict) -- 3 LDS.256 + 6 DMMA per point where
+//    the FMA version (k_elmat<DIM,3>) issued 14 LDS.256 with 5-way conflicts for its 7 entries per lane.
+//    The finished fragments go through a per-warp block in shared memory, mirrored, and leave as one coalesced store.
+// ---------------------------------------------------------------------------------------------------------------
+constexpr int W3 = 4;             // warps per CTA of the order-3 kernel
+constexpr int QC3 = 32;           // points staged per round (one per lane)
+
+template <int DIM> struct Smem3 {
+  static constexpr int ND = H1<DIM, 3>::ND, NE = ND * ND, NTRI = ND * (ND + 1) / 2, NPAIR = DIM * (DIM + 1) / 2;
+  static constexpr int NT = (ND + 7) / 8, NDP = NT * 8;
+  // double4 per staged point: ND rows + 1 (odd: the 32 writers of a row spread over all bank groups).  The last tile reads rows
+  // ND..NDP-1, i.e. the next point's first rows or, behind the last point, the factor array: finite or not, those values reach
+  // padded entries of the tiles only.
+  static constexpr int PSTR4 = (ND | 1) == ND ? ND + 2 : ND + 1;
+  static __host__ __device__ size_t tab(int nr_vol, int nr_if) { return (size_t)(nr_vol + nr_if) * 32; }
+  static __host__ __device__ size_t lut(int nr_vol, int nr_if) { return tab(nr_vol, nr_if) + (size_t)(NPAIR + 1) * NTRI * 8; }
+  static __host__ __device__ size_t stage(int nr_vol, int nr_if) { return (lut(nr_vol, nr_if) + 256 + 31) / 32 * 32; }
+  static __host__ __device__ size_t stage_per_warp() {
+    size_t a = (size_t)QC3 * PSTR4 * 32 + QC3 * 8 + 256, b = (size_t)NE * 8;       // the output block aliases the stage
+    return ((a > b ? a : b) + 31) / 32 * 32;
+  }
+  static __host__ __device__ size_t total(int nr_vol, int nr_if) { return stage(nr_vol, nr_if) + W3 * stage_per_warp(); }
+};
+
+__device__ __forceinline__ void dmma884(double &c0, double &c1, double a, double b) {
+  asm volatile("mma.sync.aligned.m8n8k4.row.col.f64.f64.f64.f64 {%0, %1}, {%2}, {%3}, {%0, %1};" : "+d"(c0), "+d"(c1) : "d"(a), "d"(b));
+}
+
+// dofs whose sign flips with the edge orientation: the second function of edge e (local dof DIM + 1 + 2 e + 1)
+template <int DIM> __device__ __forceinline__ unsigned flipped_dofs(unsigned orient) {
+  unsigned m = 0;
+#pragma unroll
+  for (int e = 0; e < H1<DIM, 3>::NEDGE; e++) m |= ((orient >> e) & 1u) << (DIM + 2 + 2 * e);
+  return m;
+}
+
+// tables of the orientation-free order-3 element, lower triangle: tab[q][tri(i, j)] = sum_p w_p d_a phi_i d_b phi_j (pair q = (a, b),
+// reference gradients), tab[NPAIR][.] = sum_p w_p phi_i phi_j.  All threads of the CTA.
+template <int DIM>
+__device__ __forceinline__ void order3_tables(double *tab, const double4 *srule_vol, int nr_vol) {
+  constexpr int ND = H1<DIM, 3>::ND, NTRI = ND * (ND + 1) / 2, NPAIR = DIM * (DIM + 1) / 2;
+  double glr[DIM + 1][DIM];
+#pragma unroll
+  for (int k = 0; k <= DIM; k++)
+#pragma unroll
+    for (int d = 0; d < DIM; d++) glr[k][d] = (k == DIM) ? -1.0 : (k == d ? 1.0 : 0.0);
+  for (int idx = threadIdx.x; idx < NTRI; idx += blockDim.x) {
+    int i = 0;
+    while ((i + 1) * (i + 2) / 2 <= idx) i++;
+    const int j = idx - i * (i + 1) / 2;
+    double acc[NPAIR + 1];
+#pragma unroll
+    for (int k = 0; k <= NPAIR; k++) acc[k] = 0.0;
+    for (int q = 0; q < nr_vol; q++) {
+      double4 r = srule_vol[q];
+      double lam[4] = {r.x, r.y, r.z, 0.0};
+      double last = 1.0;
+#pragma unroll
+      for (int k = 0; k < DIM; k++) last -= lam[k];
+      lam[DIM] = last;
+      double si, sj, gi[DIM], gj[DIM];
+      h1_shape_grad<DIM, 3>(i, lam, glr, si, gi, 0u);
+      h1_shape_grad<DIM, 3>(j, lam, glr, sj, gj, 0u);
+      int pr = 0;
+#pragma unroll
+      for (int a = 0; a < DIM; a++)
+#pragma unroll
+        for (int b = a; b < DIM; b++) {
+          acc[pr] += r.w * (a == b ? gi[a] * gj[a] : (gi[a] * gj[b] + gi[b] * gj[a]));
+          pr++;
+        }
+      acc[NPAIR] += r.w * si * sj;
+    }
+#pragma unroll
+    for (int k = 0; k <= NPAIR; k++) tab[k * NTRI + idx] = acc[k];
+  }
+}
+
+// pass 1 of the dense sink: warp per PAIR of consecutive list entries (every table value read from shared memory serves two
+// blocks).  Uncut entries of the requested domain: block from the tables (see above), one coalesced store.  Entries outside the
+// domain: zeros (same code, zero factors).  Cut entries: recorded in the work list for k_elmat3 (integer slot from an atomic counter:
+// the order of the list never reaches a value, every block is written at its own entry).  The tables are kept as full nd x nd
+// arrays here: lane l reads entry l + 32 t, conflict free.
+constexpr int W3F = 8;
+template <int DIM>
+__global__ void __launch_bounds__(W3F * 32, 3) k_elmat3_fast(ElmatArgs A, int64_t count) {
+  constexpr int ND = H1<DIM, 3>::ND, NE = ND * ND, NTRI = ND * (ND + 1) / 2, NPAIR = DIM * (DIM + 1) / 2, T = (NE + 31) / 32;
+  extern __shared__ __align__(32) unsigned char smem_raw[];
+  double4 *srule_vol = reinterpret_cast<double4 *>(smem_raw);
+  double *tab = reinterpret_cast<double *>(smem_raw + (size_t)A.nr_vol * 32);          // (NPAIR + 1) x NE
+  double *tri = tab + (NPAIR + 1) * NE;                                                // (NPAIR + 1) x NTRI, set-up only
+  for (int i = threadIdx.x; i < A.nr_vol; i += blockDim.x) srule_vol[i] = A.rule_vol[i];
+  __syncthreads();
+  order3_tables<DIM>(tri, srule_vol, A.nr_vol);
+  __syncthreads();
+  for (int idx = threadIdx.x; idx < NE; idx += blockDim.x) {
+    const int i = idx / ND, j = idx % ND, a = max(i, j), b = min(i, j);
+#pragma unroll
+    for (int q = 0; q <= NPAIR; q++) tab[q * NE + idx] = tri[q * NTRI + a * (a + 1) / 2 + b];
+  }
+  __syncthreads();
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  unsigned short eij[T];
+#pragma unroll
+  for (int t = 0; t < T; t++) {
+    const int idx = min(lane + 32 * t, NE - 1);
+    eij[t] = (unsigned short)((idx / ND) | ((idx % ND) << 8));
+  }
+  const int64_t npair = (count + 1) / 2;
+  const int64_t nwarps = (int64_t)gridDim.x * W3F;
+  for (int64_t kp = (int64_t)blockIdx.x * W3F + warp; kp < npair; kp += nwarps) {
+    double gs[2][NPAIR + 1];
+    unsigned flip[2];
+    bool store[2];
+    int np[2];
+#pragma unroll
+    for (int u = 0; u < 2; u++) {
+      const int64_t k = 2 * kp + u;
+      store[u] = false; flip[u] = 0u; np[u] = 0;
+#pragma unroll
+      for (int q = 0; q <= NPAIR; q++) gs[u][q] = 0.0;
+      if (k >= count) continue;
+      const int64_t e = A.els ? A.els[k] : k;
+      double ls[4], p[DIM + 1][DIM];
+      int vn[4];
+      load_el<DIM>(A.M, A.lset, e, ls, p, vn);
+      int mask;
+      const int dom = sign_test<DIM>(ls, mask);
+      if (dom == IF) {
+        if (lane == 0) A.work[atomicAdd(A.work_count, 1)] = (int32_t)k;
+        continue;
+      }
+      store[u] = true;
+      if (dom != A.dt) continue;
+      np[u] = A.nr_vol;
+      ElGeom<DIM> G;
+      element_geometry<DIM>(p, G);
+      const double meas = fabs(G.det);
+      double cm = A.form.cm, cs = A.form.cs;
+      if (A.form.pm | A.form.ps) {
+        double h = DIM == 2 ? sqrt(meas) : cbrt(meas);
+        cm *= ipow(h, A.form.pm); cs *= ipow(h, A.form.ps);
+      }
+      int pr = 0;
+#pragma unroll
+      for (int a = 0; a < DIM; a++)
+#pragma unroll
+        for (int b = a; b < DIM; b++) {
+          double s = 0.0;
+#pragma unroll
+          for (int d = 0; d < DIM; d++) s += G.Jinv[a][d] * G.Jinv[b][d];
+          gs[u][pr++] = meas * cs * s;
+        }
+      gs[u][NPAIR] = meas * cm;
+      flip[u] = flipped_dofs<DIM>(edge_orientation<DIM>(vn));
+    }
+    double *o0 = A.elmats + 2 * kp * NE, *o1 = o0 + NE;
+#pragma unroll
+    for (int t = 0; t < T; t++) {
+      const int idx = lane + 32 * t;
+      if (idx < NE) {
+        double s0 = 0.0, s1 = 0.0;
+#pragma unroll
+        for (int q = 0; q <= NPAIR; q++) {
+          const double w = tab[q * NE + idx];
+          s0 += gs[0][q] * w; s1 += gs[1][q] * w;
+        }
+        const int i = eij[t] & 255, j = eij[t] >> 8;
+        if (((flip[0] >> i) ^ (flip[0] >> j)) & 1u) s0 = -s0;
+        if (((flip[1] >> i) ^ (flip[1] >> j)) & 1u) s1 = -s1;
+        if (store[0]) o0[idx] = s0;
+        if (store[1]) o1[idx] = s1;
+      }
+    }
+    if (A.npts && lane < 2 && store[lane]) A.npts[2 * kp + lane] = np[lane];
+  }
+}
+
+template <int DIM, int SINK>
+__global__ void __launch_bounds__(W3 * 32) k_elmat3(ElmatArgs A, int64_t first, int64_t count) {
+  using S = Smem3<DIM>;
+  constexpr int ND = S::ND, NE = S::NE, NTRI = S::NTRI, NPAIR = S::NPAIR, NT = S::NT, PSTR4 = S::PSTR4, T = (NE + 31) / 32;
+  constexpr int NTILE = NT * (NT + 1) / 2;
+  extern __shared__ __align__(32) unsigned char smem_raw[];
+  double4 *srule_vol = reinterpret_cast<double4 *>(smem_raw);
+  double4 *srule_if = srule_vol + A.nr_vol;
+  double *tab = reinterpret_cast<double *>(smem_raw + S::tab(A.nr_vol, A.nr_if));
+  CutEntry *lut = reinterpret_cast<CutEntry *>(smem_raw + S::lut(A.nr_vol, A.nr_if));
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  unsigned char *wbase = smem_raw + S::stage(A.nr_vol, A.nr_if) + warp * S::stage_per_warp();
+  double4 *stage = reinterpret_cast<double4 *>(wbase);
+  double *facq = reinterpret_cast<double *>(wbase + (size_t)QC3 * PSTR4 * 32);
+  double *block = reinterpret_cast<double *>(wbase);               // aliases the stage (used after the contraction)
+
+  for (int i = threadIdx.x; i < A.nr_vol; i += blockDim.x) srule_vol[i] = A.rule_vol[i];
+  for (int i = threadIdx.x; i < A.nr_if; i += blockDim.x) srule_if[i] = A.rule_if[i];
+  if (threadIdx.x < 16) lut[threadIdx.x] = A.tab->e[DIM - 2][A.dt][threadIdx.x];
+  __syncthreads();
+  const bool fast = A.use_fast && A.dt != IF;
+  if (fast) {
+    order3_tables<DIM>(tab, srule_vol, A.nr_vol);
+    __syncthreads();
+  }
+
+  // full-block entries of this lane (output order) with their place in the lower-triangle tables
+  int etri[T];
+  unsigned short eij[T];
+#pragma unroll
+  for (int t = 0; t < T; t++) {
+    const int idx = min(lane + 32 * t, NE - 1);
+    const int i = idx / ND, j = idx % ND, a = max(i, j), b = min(i, j);
+    etri[t] = a * (a + 1) / 2 + b;
+    eij[t] = (unsigned short)(i | (j << 8));
+  }
+  const int kq = lane & 3, rq = lane >> 2;
+
+  if (A.d_count) count = min(count, (int64_t)*A.d_count);
+  if (A.work) count = *A.work_count;                             // pass 2 of the dense sink: the recorded entries (group = 1, first = 0)
+  const int64_t ngroups = (count + A.group - 1) / A.group;
+  const int64_t nwarps = (int64_t)gridDim.x * W3;
+  for (int64_t g = (int64_t)blockIdx.x * W3 + warp; g < ngroups; g += nwarps) {
+    const int64_t kb = first + g * A.group;
+    const int64_t ke = min(kb + (int64_t)A.group, first + count);
+    for (int64_t k0 = kb; k0 < ke; k0++) {
+      const int64_t k = A.work ? A.work[k0] : k0;
+      const int64_t kk = A.sublist ? A.sublist[k] : k;
+      const int64_t e = A.els ? A.els[kk] : kk;
+      double ls[4], p[DIM + 1][DIM];
+      int vn[4];
+      load_el<DIM>(A.M, A.lset, e, ls, p, vn);
+      const unsigned orient = edge_orientation<DIM>(vn);
+      int mask;
+      const int dom = sign_test<DIM>(ls, mask);
+      const bool cut = dom == IF;
+      const bool active = cut || dom == A.dt;
+      int np_used = 0;
+      bool in_block = false;                 // result sits in the shared-memory block (quadrature path) or in out[] (table path / zero)
+      double out[T];
+#pragma unroll
+      for (int t = 0; t < T; t++) out[t] = 0.0;
+      if (active) {
+        ElGeom<DIM> G;
+        element_geometry<DIM>(p, G);
+        const double meas = fabs(G.det);
+        double cm = A.form.cm, cs = A.form.cs, cn = A.form.cn, cd = A.form.cd;
+        if (A.form.pm | A.form.ps | A.form.pn | A.form.pd) {
+          double h = DIM == 2 ? sqrt(meas) : cbrt(meas);
+          cm *= ipow(h, A.form.pm); cs *= ipow(h, A.form.ps); cn *= ipow(h, A.form.pn); cd *= ipow(h, A.form.pd);
+        }
+        if (!cut && fast) {
+          double gs[NPAIR];
+          int pr = 0;
+#pragma unroll
+          for (int a = 0; a < DIM; a++)
+#pragma unroll
+            for (int b = a; b < DIM; b++) {
+              double s = 0.0;
+#pragma unroll
+              for (int d = 0; d < DIM; d++) s += G.Jinv[a][d] * G.Jinv[b][d];
+              gs[pr++] = meas * cs * s;
+            }
+          const double gmass = meas * cm;
+          const unsigned flip = flipped_dofs<DIM>(orient);
+#pragma unroll
+          for (int t = 0; t < T; t++) {
+            const int tr = etri[t];
+            double s = gmass * tab[NPAIR * NTRI + tr];
+#pragma unroll
+            for (int q = 0; q < NPAIR; q++) s += gs[q] * tab[q * NTRI + tr];
+            const unsigned sg = ((flip >> (eij[t] & 255)) ^ (flip >> (eij[t] >> 8))) & 1u;
+            out[t] = sg ? -s : s;
+          }
+          np_used = A.nr_vol;
+        } else {
+          in_block = true;
+          double gl[DIM + 1][DIM];
+          bary_gradients<DIM>(G, gl);
+          double nrm[3] = {0.0, 0.0, 0.0};
+          double scale = 1.0;
+          {
+            double g2 = 0.0, r2 = 0.0;
+#pragma unroll
+            for (int d = 0; d < DIM; d++) {
+              double v = 0.0;
+#pragma unroll
+              for (int m = 0; m <= DIM; m++) v += ls[m] * gl[m][d];
+              nrm[d] = v; g2 += v * v;
+            }
+#pragma unroll
+            for (int m = 0; m < DIM; m++) { double v = ls[m] - ls[DIM]; r2 += v * v; }
+            double inv = 1.0 / sqrt(g2);
+#pragma unroll
+            for (int d = 0; d < DIM; d++) nrm[d] *= inv;
+            if (cut && A.dt == IF) scale = sqrt(g2) / sqrt(r2);
+          }
+          // row kq of Q (diagonal case: Q0 = the lane's diagonal entry)
+          const bool diagq = cn == 0.0 && cd == 0.0;
+          double Q0, Q1, Q2, Q3;
+          if (diagq) { Q0 = kq == 0 ? cm : cs; Q1 = Q2 = Q3 = 0.0; }
+          else if (kq == 0) { Q0 = cm; Q1 = cn * nrm[0]; Q2 = cn * nrm[1]; Q3 = cn * nrm[2]; }
+          else {
+            const double nk = kq == 1 ? nrm[0] : (kq == 2 ? nrm[1] : nrm[2]);
+            Q0 = cn * nk;
+            Q1 = cd * nk * nrm[0] + (kq == 1 ? cs : 0.0);
+            Q2 = cd * nk * nrm[1] + (kq == 2 ? cs : 0.0);
+            Q3 = cd * nk * nrm[2] + (kq == 3 ? cs : 0.0);
+          }
+          double acc[NTILE][2];
+#pragma unroll
+          for (int t = 0; t < NTILE; t++) acc[t][0] = acc[t][1] = 0.0;
+          CutEntry E;
+          if (cut) E = lut[mask]; else { E.ns = 1; E.npt = 0; }
+          const double4 *rule = (cut && A.dt == IF) ? srule_if : srule_vol;
+          const int nr = (cut && A.dt == IF) ? A.nr_if : A.nr_vol;
+          np_used = E.ns * nr;
+          for (int s = 0; s < E.ns; s++) {
+            double P[4][3];
+            double sfac = 1.0;
+            if (cut) {
+              for (int v = 0; v < E.npt; v++) coded_point<DIM>(E.v[s][v], ls, P[v]);
+              sfac = simplex_factor(E.npt, P);
+            }
+            for (int q0 = 0; q0 < nr; q0 += QC3) {
+              const int nq = min(QC3, nr - q0);
+              if (lane < nq) {
+                double4 r = rule[q0 + lane];
+                double xi[3] = {r.x, r.y, r.z};
+                if (cut) simplex_point(E.npt, P, r, xi);
+                double lam[4] = {xi[0], xi[1], xi[2], 0.0};
+                double last = 1.0;
+#pragma unroll
+                for (int m = 0; m < DIM; m++) last -= lam[m];
+                lam[DIM] = last;
+#pragma unroll
+                for (int i = 0; i < ND; i++) {
+                  double sv, gv[DIM];
+                  h1_shape_grad<DIM, 3>(i, lam, gl, sv, gv, orient);
+                  stage[lane * PSTR4 + i] = make_double4(sv, gv[0], gv[1], DIM == 3 ? gv[DIM - 1] : 0.0);
+                }
+                facq[lane] = meas * (r.w * sfac * scale);
+              }
+              __syncwarp();
+              const double *stage1 = reinterpret_cast<const double *>(stage) + rq * 4 + kq;      // component kq of row rq
+              if (diagq) {
+                // Q = diag(c_m, c_s, c_s, c_s): B fragment = A fragment x f_q Q_kk, no second read
+#pragma unroll 2
+                for (int q = 0; q < nq; q++) {
+                  const double fd = facq[q] * Q0;
+                  double af[NT], bf[NT];
+#pragma unroll
+                  for (int c = 0; c < NT; c++) { af[c] = stage1[(q * PSTR4 + 8 * c) * 4]; bf[c] = af[c] * fd; }
+                  int t = 0;
+#pragma unroll
+                  for (int r = 0; r < NT; r++)
+#pragma unroll
+                    for (int c = 0; c <= r; c++) { dmma884(acc[t][0], acc[t][1], af[r], bf[c]); t++; }
+                }
+              } else {
+                for (int q = 0; q < nq; q++) {
+                  const double f = facq[q];
+                  double af[NT], bf[NT];
+#pragma unroll
+                  for (int c = 0; c < NT; c++) {
+                    const double4 v = stage[q * PSTR4 + 8 * c + rq];
+                    af[c] = stage1[(q * PSTR4 + 8 * c) * 4];
+                    bf[c] = f * (Q0 * v.x + Q1 * v.y + Q2 * v.z + Q3 * v.w);
+                  }
+                  int t = 0;
+#pragma unroll
+                  for (int r = 0; r < NT; r++)
+#pragma unroll
+                    for (int c = 0; c <= r; c++) { dmma884(acc[t][0], acc[t][1], af[r], bf[c]); t++; }
+                }
+              }
+              __syncwarp();
+            }
+          }
+          // fragments -> block (mirrored).  lane holds C[8r + rq][8c + 2kq + {0,1}]
+          {
+            int t = 0;
+#pragma unroll
+            for (int r = 0; r < NT; r++)
+#pragma unroll
+              for (int c = 0; c <= r; c++) {
+                const int i = 8 * r + rq;
+#pragma unroll
+                for (int h = 0; h < 2; h++) {
+                  const int j = 8 * c + 2 * kq + h;
+                  if (i < ND && j < ND) {
+                    block[i * ND + j] = acc[t][h];
+                    if (r != c) block[j * ND + i] = acc[t][h];
+                  }
+                }
+                t++;
+              }
+          }
+          __syncwarp();
+        }
+      }
+      // ---- sink ---------------------------------------------------------------------------------------------
+#pragma unroll
+      for (int t = 0; t < T; t++) {
+        const int idx = lane + 32 * t;
+        if (idx < NE) {
+          const double v = in_block ? block[idx] : out[t];
+          if constexpr (SINK == 0) A.elmats[k * NE + idx] = v;
+          else if (active) A.vals[__ldg(A.slots + k * NE + idx)] += v;
+        }
+      }
+      if (SINK == 0 && A.npts && lane == 0) A.npts[k] = np_used;
+      __syncwarp();          // the block aliases the next element's stage; coloured sink: the next element of the group may share entries
+    }
+  }
+}
+
+// ---------------------------------------------------------------------------------------------------------------
 // element vectors (SymbolicCutLFI): same staging, lanes < ND accumulate  sum_q fac_q f(x_q) phi_i(x_q)
 // SINK 0: dense elvecs[k][ND]; 1: vec[el2dof_list[k][i]] += (coloured groups)
 // ---------------------------------------------------------------------------------------------------------------
@@ -505,8 +931,63 @@ static int fill_common(const ngsx_mesh *mesh, const double *lset_v, int fe_order
   return NGSX_OK;
 }
 
+static int g_order3_fma = 0;      // debug: order 3 through the first-generation FMA kernel k_elmat<DIM,3> (A/B and parity)
+
+template <int DIM, int SINK>
+static int launch_elmat3(const ElmatArgs &A, int sm_count, int ncolors, const int64_t *h_color_ptr, int64_t nlist, cudaStream_t st) {
+  using S = Smem3<DIM>;
+  size_t smem = S::total(A.nr_vol, A.nr_if);
+  auto kern = k_elmat3<DIM, SINK>;
+  NGSX_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  int occ = 0;
+  NGSX_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, kern, W3 * 32, smem));
+  if (occ < 1) { set_error("kernel does not fit on an SM"); return NGSX_ERR_CUDA; }
+  if constexpr (SINK == 0) {
+    if (A.use_fast && A.dt != IF && !A.sublist && !A.d_count && !h_color_ptr && nlist < (int64_t)INT32_MAX) {
+      // two passes: table blocks of the uncut entries (light kernel, full occupancy), then the recorded cut entries on the tensor cores
+      int32_t *work = nullptr;
+      NGSX_CUDA(cudaMallocAsync(&work, (nlist + 1) * sizeof(int32_t), st));
+      ElmatArgs B = A;
+      B.work = work + 1; B.work_count = work;
+      cudaError_t e0 = cudaMemsetAsync(work, 0, sizeof(int32_t), st);
+      constexpr int NTRI = H1<DIM, 3>::ND * (H1<DIM, 3>::ND + 1) / 2, NPAIR = DIM * (DIM + 1) / 2;
+      const size_t smem1 = (size_t)A.nr_vol * 32 + (size_t)(NPAIR + 1) * (NTRI + H1<DIM, 3>::ND * H1<DIM, 3>::ND) * 8;
+      auto k1 = k_elmat3_fast<DIM>;
+      int occ1 = 0;
+      cudaError_t e1 = cudaFuncSetAttribute(k1, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem1);
+      if (e1 == cudaSuccess) e1 = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ1, k1, W3F * 32, smem1);
+      if (e1 == cudaSuccess && e0 == cudaSuccess && occ1 >= 1) {
+        const unsigned g1 = (unsigned)std::max<int64_t>(1, std::min<int64_t>(((nlist + 1) / 2 + W3F - 1) / W3F, (int64_t)sm_count * occ1));
+        k1<<<g1, W3F * 32, smem1, st>>>(B, nlist);
+        const unsigned g2 = (unsigned)std::max<int64_t>(1, std::min<int64_t>((nlist + W3 - 1) / W3, (int64_t)sm_count * occ));
+        kern<<<g2, W3 * 32, smem, st>>>(B, 0, nlist);
+        g_launches.fetch_add(2, std::memory_order_relaxed);
+        e1 = cudaGetLastError();
+      }
+      cudaFreeAsync(work, st);
+      NGSX_CUDA(e0);
+      NGSX_CUDA(e1);
+      if (occ1 < 1) { set_error("kernel does not fit on an SM"); return NGSX_ERR_CUDA; }
+      return NGSX_OK;
+    }
+  }
+  for (int c = 0; c < ncolors; c++) {
+    int64_t first = h_color_ptr ? h_color_ptr[c] : 0;
+    int64_t count = h_color_ptr ? h_color_ptr[c + 1] - h_color_ptr[c] : nlist;
+    if (count <= 0) continue;
+    const int64_t need = ((count + A.group - 1) / A.group + W3 - 1) / W3;
+    const unsigned grid = (unsigned)std::max<int64_t>(1, std::min<int64_t>(need, (int64_t)sm_count * occ));
+    kern<<<grid, W3 * 32, smem, st>>>(A, first, count);
+    NGSX_LAUNCH_CHECK();
+  }
+  return NGSX_OK;
+}
+
 template <int DIM, int ORDER, int SINK>
 static int launch_elmat(const ElmatArgs &A, int sm_count, int ncolors, const int64_t *h_color_ptr, int64_t nlist, cudaStream_t st) {
+  if constexpr (ORDER == 3) {
+    if (!g_order3_fma) return launch_elmat3<DIM, SINK>(A, sm_count, ncolors, h_color_ptr, nlist, st);
+  }
   using S = Smem<DIM, ORDER>;
   size_t smem = S::total(A.nr_vol, A.nr_if);
   auto kern = k_elmat<DIM, ORDER, SINK>;
@@ -1065,6 +1546,7 @@ extern "C" {
 
 // test hook: 0 disables the constant-rule path so both paths can be compared on the GPU
 void ngsx_debug_set_fast_path(int on) { g_use_fast = on; }
+void ngsx_debug_set_order3_fma(int on) { g_order3_fma = on; }
 
 // measurement hook: when on, ngsx_assemble_csr_rows_h1 records events around its kernels (a ring of 64 event sets, so the
 // caller need not synchronise every step); ngsx_debug_get_timing waits for the last call and returns the mean over the calls
@@ -1113,7 +1595,7 @@ int ngsx_elmat_h1(const ngsx_mesh *mesh, const double *lset_v, int fe_order, int
   fill_form(h_form, A.form);
   A.els = els; A.group = 1; A.use_fast = g_use_fast && h_form->c_nitsche == 0.0 && h_form->c_dndn == 0.0;
   A.elmats = elmats; A.npts = npts;
-  if (take_packed_output()) { set_error("elmat_h1: packed output is not served by this entry point yet"); return NGSX_ERR_UNSUPPORTED; }
+  if (take_packed_output()) { set_error("elmat_h1: packed output is not served by this entry point (measured for order 3: the scattered 160-byte row stores cost the producer more than the packed gather saves)"); return NGSX_ERR_UNSUPPORTED; }
   return dispatch_elmat<0>(A, fe_order, dd->sm_count, 1, nullptr, nlist, as_stream(stream));
 }
 

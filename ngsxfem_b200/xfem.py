@@ -828,6 +828,7 @@ class BilinearForm:
                 else:
                     if getattr(plan, "mats", None) is None:
                         plan.mats = torch.empty((n, fes.nd * fes.nd), dtype=torch.float64, device=fes.mesh.device)
+                    # order 3: k_elmat3_fast (sign-flipped constant-rule tables) + k_elmat3 (DMMA contraction on the cut elements)
                     check(L.ngsx_elmat_h1(mesh_c, _ptr(lv), fes.order, integ.dt, integ.intorder(fes.order), ctypes.byref(integ.form), n,
                                           _ptr(plan.els), _ptr(plan.mats), None, _stream()))
                     check(L.ngsx_assemble_csr_rows_mats(plan.handle, _ptr(plan.mats), 0 if overwrite else 1, _ptr(self.mat.vals), _stream()))

@@ -1363,6 +1363,46 @@ def test_order3_single_elements_vertex_permutations(X, golden_single, dim):
         assert np.abs(f.vec.cpu().numpy() - want).max() <= RTOL * np.abs(want).max()
 
 
+@pytest.mark.parametrize("dim,nx", [(2, 12), (3, 5)])
+def test_order3_tensor_core_kernel_against_fma_kernel(X, dim, nx):
+    """g-1: k_elmat3 (sign-flipped constant-rule tables on uncut elements, DMMA contraction with the form's 4 x 4 matrix on cut
+    elements) against the first-generation FMA kernel k_elmat<DIM,3> (itself checked against the oracle above), including the
+    Nitsche / dn.dn terms and a power of h, with the constant-rule path on and off."""
+    m = X.meshes.MakeStructured2DMesh(nx) if dim == 2 else X.meshes.MakeStructured3DMesh(nx)
+    mesh = X.ngs.Mesh(m)
+    gf = X.ngs.GridFunction(X.ngs.H1(mesh, order=1))
+    X.xfem.InterpolateToP1(X.ngs.SphereLevelset((0.5,) * dim, 0.35), gf)
+    gf.vec += dev(1e-3 * np.random.default_rng(5).uniform(-1, 1, mesh.nv))
+    L = X.lib.load()
+    st = torch.cuda.current_stream().cuda_stream
+    els = torch.arange(mesh.ne, dtype=torch.int32, device="cuda")
+    nd = 10 if dim == 2 else 20
+    forms = [X.lib.FormH1(1.3, 0.7, 0.0, 0.0, 0, 0, 0, 0), X.lib.FormH1(1.3, 0.7, 0.0, 0.0, 1, -1, 0, 0),
+             X.lib.FormH1(0.4, 0.9, -0.8, 0.3, 0, 0, -1, 1)]
+    try:
+        for f in forms:
+            for dt in (NEG, POS, IF):
+                res = {}
+                for fma, fast in ((1, 1), (0, 1), (0, 0)):
+                    L.ngsx_debug_set_order3_fma(fma)
+                    L.ngsx_debug_set_fast_path(fast)
+                    em = torch.full((mesh.ne, nd * nd), float("nan"), dtype=torch.float64, device="cuda")
+                    npts = torch.zeros(mesh.ne, dtype=torch.int32, device="cuda")
+                    X.lib.check(L.ngsx_elmat_h1(ctypes.byref(mesh.c_struct()), gf.vec.data_ptr(), 3, dt, 6, ctypes.byref(f), mesh.ne, els.data_ptr(),
+                                                em.data_ptr(), npts.data_ptr(), st))
+                    res[(fma, fast)] = (em.cpu().numpy().reshape(-1, nd, nd), npts.cpu().numpy())
+                ref, rn = res[(1, 1)]
+                assert np.abs(ref).max() > 0
+                for key in ((0, 1), (0, 0)):
+                    got, gn = res[key]
+                    assert np.array_equal(gn, rn)
+                    assert np.allclose(got, np.swapaxes(got, 1, 2), rtol=0, atol=1e-13 * np.abs(ref).max())
+                    assert relerr_rows(got, ref) <= RTOL, (dt, key)
+    finally:
+        L.ngsx_debug_set_order3_fma(0)
+        L.ngsx_debug_set_fast_path(1)
+
+
 @pytest.mark.parametrize("dim,fo", [(2, 1), (2, 2), (3, 1), (3, 2)])
 def test_packed_rows_equal_dense_blocks(X, dim, fo):
     """the two sources of the matrix gather (dense blocks fetched per lane / packed rows written by the producer at the slots of

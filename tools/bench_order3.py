@@ -25,6 +25,9 @@ def main():
     xf.InterpolateToP1(ngs.SphereLevelset((0.5, 0.5, 0.5), 0.35), gf)
     ci = xf.CutInfo(mesh, gf)
     ev = lambda: torch.cuda.Event(enable_timing=True)
+    import bench
+    clocks = bench.ClockSampler(0)
+    clocks.start()
 
     def timed(fn):
         for _ in range(3):
@@ -38,8 +41,8 @@ def main():
         torch.cuda.synchronize()
         return a.elapsed_time(b) / steps
 
-    out = {"workload": f"H1 order 3: {mesh.ne} Kuhn tets, sphere r = 0.35, NEG grad-grad + mass restricted to HASNEG (order-6 rules: 24 points per "
-                       "uncut tet)", "ne": mesh.ne, "ms": {}}
+    out = {"workload": f"H1 order 3: {mesh.ne} Kuhn tets, sphere r = 0.35, NEG grad-grad + mass restricted to HASNEG (order-6 rules: 64 points per "
+                       "tet / sub-tet)", "ne": mesh.ne, "ms": {}}
     for fo in (2, 3):
         Vh = ngs.H1(mesh, order=fo)
         u, v = Vh.TnT()
@@ -55,11 +58,16 @@ def main():
         if fo == 3:
             mc = ctypes.byref(mesh.c_struct())
             st = ctypes.c_void_p(torch.cuda.current_stream().cuda_stream)
-            out["ms"]["k_elmat<3,3>"] = timed(lambda: L.ngsx_elmat_h1(mc, gf.vec.data_ptr(), 3, 0, 6, ctypes.byref(a.integrators[0].form), n,
-                                                                      plan.els.data_ptr(), plan.mats.data_ptr(), None, st))
-            out["ms"]["k_rows_mats<20>"] = timed(lambda: L.ngsx_assemble_csr_rows_mats(plan.handle, plan.mats.data_ptr(), 0, a.mat.vals.data_ptr(), st))
+            mats = plan.mats
+            dense = lambda: L.ngsx_elmat_h1(mc, gf.vec.data_ptr(), 3, 0, 6, ctypes.byref(a.integrators[0].form), n, plan.els.data_ptr(), mats.data_ptr(), None, st)
+            out["ms"]["k_elmat3_fast + k_elmat3 (dense blocks)"] = timed(dense)
+            L.ngsx_debug_set_order3_fma(1)
+            out["ms"]["k_elmat<3,3> (first-generation FMA kernel, dense blocks)"] = timed(dense)
+            L.ngsx_debug_set_order3_fma(0)
+            dense()
+            out["ms"]["k_rows_mats<20> (dense blocks)"] = timed(lambda: L.ngsx_assemble_csr_rows_mats(plan.handle, mats.data_ptr(), 0, a.mat.vals.data_ptr(), st))
             out["elements_per_s_P3_assemble"] = n / (out["ms"]["Assemble(P3)"] * 1e-3)
-            out["k_elmat_algorithmic_GBs"] = n * (16 + 96 + 32 + 3200) / (out["ms"]["k_elmat<3,3>"] * 1e-3) / 1e9
+            out["producer_algorithmic_GBs"] = n * (16 + 96 + 32 + 3200) / (out["ms"]["k_elmat3_fast + k_elmat3 (dense blocks)"] * 1e-3) / 1e9
             try:
                 from oracle import orc
                 els = plan.els.cpu().numpy()
@@ -74,6 +82,7 @@ def main():
                                        "sample": f"{len(sample)} of the {len(els)} listed elements, element matrices only (orc_elmat_mesh, OpenMP)"}
             except Exception as exc:
                 out["cpu_baseline"] = {"error": f"{type(exc).__name__}: {str(exc)[:200]}"}
+    out["clocks"] = clocks.stop()
     print(json.dumps(out))
 
 
