@@ -19,7 +19,7 @@
  *   ngsx_assemble_csr_h1      NGS/comp/bilinearform.cpp:1117-1575 + NGS/linalg/sparsematrix_impl.hpp:63-103
  *   ngsx_assemble_vec_h1      NGS/comp/linearform.cpp:209-243
  *   ngsx_integrate            cutint/python_cutint.cpp:20-72        (IntegrateX)
- *   ngsx_st_rule_count/_fill, ngsx_st_integrate
+ *   ngsx_st_rule_count/_fill, ngsx_st_integrate, ngsx_st_elmat_h1, ngsx_st_classify
  *                             cutint/spacetimecutrule.cpp:6-196, cutint/xintegration.cpp:38-58 (time_order >= 0)
  *   ngsx_facets_neighbor_types[_periodic], ngsx_elements_with_neighbor_facets, ngsx_dofs_of_elements
  *                             xfem/cutinfo.cpp:191-329              (xfem/python_xfem.cpp:168-318; GetDofsOfFacets = ngsx_dofs_of_elements
@@ -295,11 +295,11 @@ int ngsx_integrate_deformed(const ngsx_mesh *mesh, const ngsx_deformation *defo,
 
 /* ---- (f-3) space-time cut quadrature -----------------------------------------------------------------------------
  * SpaceTimeCutIntegrationRule (cutint/spacetimecutrule.cpp:98-196) for a level set that is P1 in space and nodal of order
- * ntime_dofs - 1 (0..2) in the reference time: lset_st [ntime_dofs][nv], time-major like SpaceTimeFESpace::GetDofNrs
+ * ntime_dofs - 1 (0..5: NodalTimeFE, Gauss-Lobatto nodes, spacetime/SpaceTimeFE.cpp:150-173) in the reference time: lset_st [ntime_dofs][nv], time-major like SpaceTimeFESpace::GetDofNrs
  * (spacetime/SpaceTimeFESpace.cpp:109-122).  npts[e] = size of the element's space-time rule (0 where the reference returns
  * nullptr); points (reference coordinates), reference times and weights (the reference's wei_arr: w_space * w_time * (t1-t0),
- * IF weights carry |F^-T n|) are written at offs[e] in the reference's emission order.  Time elements of order > 2 (bisection
- * root finding, spacetimecutrule.cpp:46-95) are NGSX_ERR_UNSUPPORTED. */
+ * IF weights carry |F^-T n|) are written at offs[e] in the reference's emission order.  Roots in time: closed forms for orders 1, 2
+ * (spacetimecutrule.cpp:6-45), the reference's 50 subdivisions + secant / bisection refinement above (:46-95). */
 int ngsx_st_rule_count(const ngsx_mesh *mesh, const double *lset_st, int ntime_dofs, int dt, int order_space, int order_time,
                        int32_t *npts, void *stream);
 int ngsx_st_rule_fill(const ngsx_mesh *mesh, const double *lset_st, int ntime_dofs, int dt, int order_space, int order_time,
@@ -309,6 +309,18 @@ int ngsx_st_rule_fill(const ngsx_mesh *mesh, const double *lset_st, int ntime_do
  * fixed-shape reduction, bitwise reproducible. */
 int ngsx_st_integrate(const ngsx_mesh *mesh, const double *lset_st, int ntime_dofs, int dt, int order_space, int order_time,
                       const ngsx_poly *h_f, const int32_t *h_texp, double *out, void *stream);
+
+/* Space-time element matrices: T_CalcElementMatrixAdd (xfem/symboliccutbfi.cpp:73-315) on the tensor-product element SpaceTimeFE
+ * (spacetime/SpaceTimeFE.cpp:29-113: CalcShape, CalcDShape, CalcDtShape) = H1 of order fe_order (1..2) x NodalTimeFE with
+ * fe_time_dofs dofs (1..6), dof j * nd_space + i, integrated with the space-time cut rule above:
+ * elmats[k][(test)][(trial)] = sum_q |det J| w_q (c_mass u v + c_stiff grad u . grad v + c_dt dt(u) v), dt = derivative with respect
+ * to the REFERENCE time (ngsxfem's dt(), python/__init__.py).  els: list of elements (NULL = all); blocks of elements with an empty
+ * rule are zero. */
+int ngsx_st_elmat_h1(const ngsx_mesh *mesh, const double *lset_st, int ntime_dofs, int fe_order, int fe_time_dofs, int dt, int order_space,
+                     int order_time, double c_mass, double c_stiff, double c_dt, int64_t nlist, const int32_t *els, double *elmats, void *stream);
+/* CutInformation::Update with time_order >= 0 (xfem/cutinfo.cpp:79-111): part volumes of the space-time prism from the POS and NEG
+ * space-time rules of order 0 in space and time_order in time -> dom [ne] int8 (NEG / POS / IF), cut ratio [ne] */
+int ngsx_st_classify(const ngsx_mesh *mesh, const double *lset_st, int ntime_dofs, int time_order, int8_t *dom, double *ratio, void *stream);
 
 /* ---- (f-5) quadrilaterals / hexahedra ------------------------------------------------------------------------------
  * LevelsetCutQuadrilateral (cutint/straightcutrule.cpp:206-501, policy FIND_OPTIMAL) and the ET_QUAD / ET_HEX branch of

@@ -114,6 +114,9 @@ SIGNATURES = {
                                    c_void_p, c_int, c_void_p, c_void_p]),
     "ngsx_st_rule_count": (c_int, [ctypes.POINTER(Mesh), c_void_p, c_int, c_int, c_int, c_int, c_void_p, c_void_p]),
     "ngsx_st_rule_fill": (c_int, [ctypes.POINTER(Mesh), c_void_p, c_int, c_int, c_int, c_int, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p]),
+    "ngsx_st_elmat_h1": (c_int, [ctypes.POINTER(Mesh), c_void_p, c_int, c_int, c_int, c_int, c_int, c_int, c_double, c_double, c_double, c_i64,
+                                 c_void_p, c_void_p, c_void_p]),
+    "ngsx_st_classify": (c_int, [ctypes.POINTER(Mesh), c_void_p, c_int, c_int, c_void_p, c_void_p, c_void_p]),
     "ngsx_st_integrate": (c_int, [ctypes.POINTER(Mesh), c_void_p, c_int, c_int, c_int, c_int, ctypes.POINTER(Poly), ctypes.POINTER(c_i32),
                                   c_void_p, c_void_p]),
     "ngsx_assemble_csr_rows_mats": (c_int, [c_void_p, c_void_p, c_int, c_void_p, c_void_p]),

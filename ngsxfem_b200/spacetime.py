@@ -10,16 +10,20 @@ from . import _lib
 from ._lib import NgsxError, check
 from .ngs import FESpace, GridFunction, H1, Poly, TPoly, _ptr, _stream
 
-_NODES = {0: [0.0], 1: [0.0, 1.0], 2: [0.0, 0.5, 1.0]}          # NodalTimeFE::CalcInterpolationPoints, spacetime/SpaceTimeFE.cpp:150-160
+_S5, _S37, _S7 = 5.0 ** 0.5, (3.0 / 7.0) ** 0.5, 7.0 ** 0.5
+_NODES = {0: [0.0], 1: [0.0, 1.0], 2: [0.0, 0.5, 1.0],          # NodalTimeFE::CalcInterpolationPoints, spacetime/SpaceTimeFE.cpp:150-173
+          3: [0.0, 0.5 * (1.0 - 1.0 / _S5), 0.5 * (1.0 + 1.0 / _S5), 1.0],
+          4: [0.0, 0.5 * (1.0 - _S37), 0.5, 0.5 * (1.0 + _S37), 1.0],
+          5: [0.0, 0.5 * (1.0 - (1.0 / 3.0 + 2.0 * _S7 / 21.0) ** 0.5), 0.5 * (1.0 - (1.0 / 3.0 - 2.0 * _S7 / 21.0) ** 0.5),
+              0.5 * (1.0 + (1.0 / 3.0 - 2.0 * _S7 / 21.0) ** 0.5), 0.5 * (1.0 + (1.0 / 3.0 + 2.0 * _S7 / 21.0) ** 0.5), 1.0]}
 
 
 class ScalarTimeFE:
-    """spacetime/python_spacetime.cpp: nodal time element of the given order (orders 0..2 on the CUDA path)"""
+    """spacetime/python_spacetime.cpp: nodal time element of the given order (0..5, the orders NodalTimeFE has nodes for)"""
 
     def __init__(self, order: int = 1, skip_first_node: bool = False, only_first_node: bool = False):
         if skip_first_node or only_first_node or order not in _NODES:
-            raise NgsxError(-2, "ScalarTimeFE: orders 0..2 without node skipping are on the CUDA path (order > 2 needs the bisection "
-                                "root finding of cutint/spacetimecutrule.cpp:46-95)")
+            raise NgsxError(-2, "ScalarTimeFE: orders 0..5 without node skipping are on the CUDA path")
         self.order = order
         self.nodes = _NODES[order]
         self.ndof = order + 1
@@ -29,10 +33,20 @@ class SpaceTimeFESpace(FESpace):
     """tensor-product space: dof = k * ndof_space + space dof (spacetime/SpaceTimeFESpace.cpp:109-122)"""
 
     def __init__(self, space: H1, tfe: ScalarTimeFE, **_):
-        if not isinstance(space, H1) or space.order != 1:
-            raise NgsxError(-2, "SpaceTimeFESpace: the space-time level set must be P1 in space")
+        if not isinstance(space, H1) or space.order not in (1, 2):
+            raise NgsxError(-2, "SpaceTimeFESpace: H1 of order 1..2 in space is on the CUDA path (the level set must be P1 in space)")
         self.space, self.tfe, self.mesh, self.order = space, tfe, space.mesh, space.order
         self.ndof = space.ndof * tfe.ndof
+        self.nd = space.nd * tfe.ndof
+        self._el2dof = None
+
+    @property
+    def el2dof(self):
+        """[ne][ntd * nd_space]: dof (j, i) of SpaceTimeFE = j * ndof_space + space dof i (SpaceTimeFESpace::GetDofNrs)"""
+        if self._el2dof is None:
+            s = self.space.el2dof.long()
+            self._el2dof = torch.cat([s + j * self.space.ndof for j in range(self.tfe.ndof)], dim=1).to(torch.int32).contiguous()
+        return self._el2dof
 
     def TimeFE_nodes(self):
         return list(self.tfe.nodes)
@@ -68,6 +82,8 @@ def lset_st(levelset):
     """(device vector, number of time dofs) of a level-set GridFunction for the space-time rule; a plain P1 GridFunction is
     constant in time (the reference warns and does the same, cutint/xintegration.cpp:44-55)"""
     if isinstance(levelset, GridFunction) and isinstance(levelset.space, SpaceTimeFESpace):
+        if levelset.space.order != 1:
+            raise NgsxError(-2, "the space-time level set must be P1 in space")
         return levelset.vec, levelset.space.tfe.ndof
     if isinstance(levelset, GridFunction) and levelset.space.order == 1:
         return levelset.vec, 1
@@ -110,3 +126,75 @@ def cut_rule(levelset, mesh, domain_type, order_space, order_time):
     w = torch.zeros(max(n, 1), dtype=torch.float64, device=dev)
     check(L.ngsx_st_rule_fill(mc, _ptr(vec), ntd, int(domain_type), order_space, order_time, _ptr(offs), _ptr(pts), _ptr(tq), _ptr(w), _stream()))
     return npts, offs, pts[:n], tq[:n], w[:n]
+
+
+def classify(levelset, mesh, time_order):
+    """CutInformation::Update with time_order >= 0 (xfem/cutinfo.cpp:79-111): (dom [ne] int8, cut ratio [ne])"""
+    vec, ntd = lset_st(levelset)
+    dom = torch.zeros(mesh.ne, dtype=torch.int8, device=mesh.device)
+    ratio = torch.zeros(mesh.ne, dtype=torch.float64, device=mesh.device)
+    check(_lib.load().ngsx_st_classify(ctypes.byref(mesh.c_struct()), _ptr(vec), ntd, int(time_order), _ptr(dom), _ptr(ratio), _stream()))
+    return dom, ratio
+
+
+def elmats(fes: SpaceTimeFESpace, levelset, domain_type, c_mass=0.0, c_stiff=0.0, c_dt=0.0, order_space=None, order_time=None, els=None,
+           out=None):
+    """space-time element matrices of  c_mass u v + c_stiff grad(u) grad(v) + c_dt dt(u) v  on SpaceTimeFE (spacetime/SpaceTimeFE.cpp:29-113)
+    with the space-time cut rule: [n][N][N], N = fes.nd, rows = test functions.  Default orders as SymbolicCutBFI on a space-time
+    space would pick them: 2 * order in space and in time."""
+    mesh = fes.mesh
+    vec, ntd = lset_st(levelset)
+    os_ = 2 * fes.space.order if order_space is None else order_space
+    ot = 2 * fes.tfe.order if order_time is None else order_time
+    n = mesh.ne if els is None else els.numel()
+    if out is None:
+        out = torch.empty((n, fes.nd, fes.nd), dtype=torch.float64, device=mesh.device)
+    check(_lib.load().ngsx_st_elmat_h1(ctypes.byref(mesh.c_struct()), _ptr(vec), ntd, fes.space.order, fes.tfe.ndof, int(domain_type), os_, ot,
+                                       float(c_mass), float(c_stiff), float(c_dt), n, _ptr(els), _ptr(out), _stream()))
+    return out
+
+
+class SpaceTimeOperator:
+    """assembled space-time operator of one cut integrator on SpaceTimeFESpace: CSR pattern from the space-time dof table
+    (GetGraph), owner-computes row plan, element blocks from ngsx_st_elmat_h1, gather without atomics (ngsx_assemble_csr_rows_mats).
+    Pattern and plan are built once; Assemble() re-evaluates the blocks for the current level set."""
+
+    def __init__(self, fes: SpaceTimeFESpace, levelset, domain_type, c_mass=0.0, c_stiff=0.0, c_dt=0.0, order_space=None, order_time=None):
+        from .ngs import CSRMatrix
+        L = _lib.load()
+        self.fes, self.levelset, self.dt = fes, levelset, int(domain_type)
+        self.coef = (c_mass, c_stiff, c_dt)
+        self.orders = (order_space, order_time)
+        tab = fes.el2dof
+        dev = fes.mesh.device
+        g = ctypes.c_void_p()
+        check(L.ngsx_csr_graph_create(fes.ndof, ctypes.byref(g)))
+        try:
+            check(L.ngsx_csr_graph_add_table(g, tab.shape[0], tab.shape[1], _ptr(tab), _stream()))
+            nnz = ctypes.c_int64(0)
+            check(L.ngsx_csr_graph_finalize(g, ctypes.byref(nnz), _stream()))
+            rowptr = torch.empty(fes.ndof + 1, dtype=torch.int64, device=dev)
+            colidx = torch.empty(nnz.value, dtype=torch.int32, device=dev)
+            check(L.ngsx_csr_graph_export(g, _ptr(rowptr), _ptr(colidx), _stream()))
+            torch.cuda.current_stream().synchronize()
+        finally:
+            L.ngsx_csr_graph_destroy(g)
+        self.mat = CSRMatrix(fes.ndof, rowptr, colidx, torch.zeros(nnz.value, dtype=torch.float64, device=dev))
+        h = ctypes.c_void_p()
+        check(L.ngsx_rowplan_create(tab.shape[0], tab.shape[1], _ptr(tab), fes.ndof, _ptr(rowptr), _ptr(colidx), 0, fes.ndof, ctypes.byref(h),
+                                    _stream()))
+        self.plan = h
+        self.blocks = torch.empty((tab.shape[0], fes.nd, fes.nd), dtype=torch.float64, device=dev)
+
+    def Assemble(self):
+        elmats(self.fes, self.levelset, self.dt, *self.coef, order_space=self.orders[0], order_time=self.orders[1], out=self.blocks)
+        check(_lib.load().ngsx_assemble_csr_rows_mats(self.plan, _ptr(self.blocks), 0, _ptr(self.mat.vals), _stream()))
+        return self
+
+    def __del__(self):
+        try:
+            if self.plan is not None:
+                _lib.load().ngsx_rowplan_destroy(self.plan)
+                self.plan = None
+        except Exception:
+            pass

@@ -78,10 +78,17 @@ class CutInfo:
         return self.mesh
 
     def Update(self, levelset, time_order: int = -1, heapsize: int = 1000000, node_marks: bool = False):
-        if time_order >= 0:
-            raise NgsxError(-2, "space-time CutInfo (time_order >= 0) is outside the CUDA path")
-        lv = _lset_vec(levelset)
         L = _lib_()
+        if time_order >= 0:                                          # space-time prisms: part volumes from the space-time rules
+            from . import spacetime
+            self.dom, self.ratio = spacetime.classify(levelset, self.mesh, time_order)
+            d = self.dom
+            for cdt, mask in ((1, d == NEG), (2, d == POS), (3, (d == NEG) | (d == POS)), (4, d == IF), (5, (d == NEG) | (d == IF)),
+                              (6, (d == POS) | (d == IF)), (7, torch.ones_like(d, dtype=torch.bool))):
+                self.words[cdt] = BitArray.from_bool(mask).words
+            self._bnd = None
+            return self
+        lv = _lset_vec(levelset)
         if getattr(self.mesh, "tensor", False):                      # quadrilaterals / hexahedra (row f-5)
             check(L.ngsx_q_classify(ctypes.byref(self.mesh.c_struct()), _ptr(lv), _ptr(self.dom), _ptr(self.ratio), _ptr(self.err), _stream()))
             d = self.dom

@@ -317,9 +317,54 @@ int orc_cutinfo_element(int dim, const double *pmat, const double *ls, double *r
 }
 
 /* ------------------------------------------------------------------ space-time cut rule */
+#define ST_MAXTD 6
+/* NodalTimeFE::CalcInterpolationPoints (spacetime/SpaceTimeFE.cpp:150-173) */
+static void st_nodes(int ntd, double *nd)
+{
+  nd[0] = 0.0;
+  switch (ntd - 1) {
+    case 1: nd[1] = 1.0; break;
+    case 2: nd[1] = 0.5; nd[2] = 1.0; break;
+    case 3: nd[1] = 0.5*(1.0 - 1.0/sqrt(5.0)); nd[2] = 0.5*(1.0 + 1.0/sqrt(5.0)); nd[3] = 1.0; break;
+    case 4: nd[1] = 0.5*(1.0 - sqrt(3.0/7.0)); nd[2] = 0.5; nd[3] = 0.5*(1.0 + sqrt(3.0/7.0)); nd[4] = 1.0; break;
+    case 5: nd[1] = 0.5*(1.0 - sqrt(1.0/3.0 + 2.0*sqrt(7.0)/21.0)); nd[2] = 0.5*(1.0 - sqrt(1.0/3.0 - 2.0*sqrt(7.0)/21.0));
+            nd[3] = 0.5*(1.0 + sqrt(1.0/3.0 - 2.0*sqrt(7.0)/21.0)); nd[4] = 0.5*(1.0 + sqrt(1.0/3.0 + 2.0*sqrt(7.0)/21.0));
+            nd[5] = 1.0; break;
+    default: break;
+  }
+}
+
+/* NodalTimeFE::CalcShape / CalcDShape: Lagrange_Pol (spacetime/SpaceTimeFE.hpp:86-95) on a value + derivative pair (AutoDiff<1>) */
+static void st_lagrange(int ntd, double x, double *sh, double *dsh)
+{
+  double nd[ST_MAXTD];
+  st_nodes(ntd, nd);
+  for (int i = 0; i < ntd; i++) {
+    double val = 1.0, der = 0.0;
+    for (int j = 0; j < ntd; j++)
+      if (j != i) {
+        double f = (x - nd[j]) / (nd[i] - nd[j]), df = 1.0 / (nd[i] - nd[j]);
+        der = der * f + val * df;
+        val *= f;
+      }
+    sh[i] = val;
+    if (dsh) dsh[i] = der;
+  }
+}
+
+static double st_eval(int ntd, const double *li, double xi)
+{
+  double sh[ST_MAXTD], v = 0;
+  st_lagrange(ntd, xi, sh, NULL);
+  for (int k = 0; k < ntd; k++) v += li[k] * sh[k];
+  return v;
+}
+
 /* cutint/spacetimecutrule.cpp:6-96 root_finding: zeros in (0,1) of the level-set trace of ONE vertex in time; nodal time element
- * of order 0..2 (spacetime/SpaceTimeFE.cpp:150-160: nodes 0 | 0,1 | 0,1/2,1).  Same expressions as the reference, including
- * the division by a = 0 when the order-2 data is linear in time (IEEE inf / nan -> no root). */
+ * of order 0..5.  Orders 1, 2: the closed forms, same expressions as the reference, including the division by a = 0 when the
+ * order-2 data is linear in time (IEEE inf / nan -> no root).  Orders >= 3 (:46-95): 50 subdivisions; a value that is exactly 0
+ * at a subdivision point is a root; every sign change is refined by <= 70 rounds of "secant point with |value| < 5e-16 ends,
+ * else bisection step"; roots in the order "exact zeros first, then the refined intervals" (values are sorted by the caller). */
 static int st_roots(int ntd, const double *li, double *roots)
 {
   int n = 0;
@@ -336,6 +381,33 @@ static int st_roots(int ntd, const double *li, double *roots)
       if (x1 < 1 && x1 > 0) roots[n++] = x1;
       if (x2 < 1 && x2 > 0) roots[n++] = x2;
     }
+  } else if (ntd > 3) {
+    const int subdivs = 50, bisection_iterations = 70;
+    const double delta_x = 1./subdivs;
+    double vals[51], ia[51];
+    int ni = 0;
+    for (int i = 0; i < subdivs + 1; i++) {
+      double xi = delta_x * i;
+      vals[i] = st_eval(ntd, li, xi);
+      if (vals[i] == 0 && n < ST_MAXTD - 1) roots[n++] = xi;
+      if (i >= 1) if (vals[i-1] * vals[i] < 0) ia[ni++] = xi - delta_x;
+    }
+    for (int m = 0; m < ni && n < ST_MAXTD - 1; m++) {
+      double a = ia[m], b = ia[m] + delta_x, x_mid;
+      double aval = st_eval(ntd, li, a), bval = st_eval(ntd, li, b);
+      for (int j = 0; j < bisection_iterations; j++) {
+        const double x_lin = a - aval*(b - a)/(bval - aval);
+        double val = st_eval(ntd, li, x_lin);
+        if (2*fabs(val) < 1e-15) { a = b = x_lin; break; }
+        x_mid = 0.5*(a + b);
+        val = st_eval(ntd, li, x_mid);
+        if (val == 0) break;
+        if (val * aval < 0) { b = x_mid; bval = val; }
+        else if (val * bval < 0) { a = x_mid; aval = val; }
+        else break;                                    /* reference: throws "Strange sign structure during bisection!" */
+      }
+      roots[n++] = 0.5*(a + b);
+    }
   }
   return n;
 }
@@ -344,7 +416,8 @@ static void st_time_shape(int ntd, double t, double *sh)
 {
   if (ntd == 1) sh[0] = 1.0;
   else if (ntd == 2) { sh[0] = 1.0 - t; sh[1] = t; }
-  else { sh[0] = (1 - t) * (1 - 2*t) ; sh[1] = 4*t*(1 - t); sh[2] = t*(2*t - 1); }
+  else if (ntd == 3) { sh[0] = (1 - t) * (1 - 2*t) ; sh[1] = 4*t*(1 - t); sh[2] = t*(2*t - 1); }
+  else st_lagrange(ntd, t, sh, NULL);
 }
 
 /* cutint/spacetimecutrule.cpp:98-196 SpaceTimeCutIntegrationRule.  lset_st [ntd][dim+1] (time-major, SpaceTimeFESpace::GetDofNrs);
@@ -353,13 +426,13 @@ static void st_time_shape(int ntd, double t, double *sh)
 int orc_st_cut_rule(int dim, const double *pmat, const double *lset_st, int ntd, int dt, int order_time, int order_space,
                     double *pts3, double *tq, double *wts, int cap)
 {
-  if (ntd < 1 || ntd > 3) return ORC_UNSUP;
+  if (ntd < 1 || ntd > ST_MAXTD) return ORC_UNSUP;
   const int nv = dim + 1;
-  double cp[16];
+  double cp[2 + 4*ST_MAXTD];
   int ncp = 0;
   cp[ncp++] = 0.0; cp[ncp++] = 1.0;
   for (int i = 0; i < nv; i++) {
-    double li[3], r[2];
+    double li[ST_MAXTD], r[ST_MAXTD];
     for (int k = 0; k < ntd; k++) li[k] = lset_st[k*nv + i];
     int nr = st_roots(ntd, li, r);
     for (int k = 0; k < nr; k++) cp[ncp++] = r[k];
@@ -377,7 +450,7 @@ int orc_st_cut_rule(int dim, const double *pmat, const double *lset_st, int ntd,
     const double t0 = cp[i], t1 = cp[i+1];
     for (int q = 0; q < nrt; q++) {
       const double t = t0 + rt[q][0] * (t1 - t0);
-      double sh[3], ls[4];
+      double sh[ST_MAXTD], ls[4];
       st_time_shape(ntd, t, sh);
       for (int v = 0; v < nv; v++) {
         double d = 0;
@@ -973,6 +1046,61 @@ double orc_integrate_mesh(int dim, int64_t ne, const int32_t *el2v, const double
   return sum;
 }
 
+/* Space-time element matrix: T_CalcElementMatrixAdd (xfem/symboliccutbfi.cpp:73-315) with the space-time rule and the tensor-product
+ * element SpaceTimeFE (spacetime/SpaceTimeFE.cpp:29-113): shape[j*nd_s + i] = phi_i(x) tau_j(tref) (CalcShape :29-55), spatial
+ * gradient grad phi_i tau_j (CalcDShape :57-84), reference-time derivative phi_i tau_j' (CalcDtShape :88-113); tau = NodalTimeFE of
+ * order ntd_fe - 1.  elmat[(test)][(trial)] = sum_q |det J| w_q (c_m u v + c_s grad u . grad v + c_t dt(u) v).  lset_st [ntd][dim+1]. */
+int orc_st_elmat_h1(int dim, int fe_order, int ntd_fe, const double *pmat, const double *lset_st, int ntd, int dt, int order_time,
+                    int order_space, double c_mass, double c_stiff, double c_dt, double *elmat)
+{
+  static _Thread_local double pts[3*ORC_MAXPTS], w[ORC_MAXPTS], tq[ORC_MAXPTS];
+  if (ntd_fe < 1 || ntd_fe > ST_MAXTD) return ORC_UNSUP;
+  int np = orc_st_cut_rule(dim, pmat, lset_st, ntd, dt, order_time, order_space, pts, tq, w, ORC_MAXPTS);
+  int nds = orc_h1_ndof(dim, fe_order), N = nds * ntd_fe;
+  for (int i = 0; i < N*N; i++) elmat[i] = 0;
+  if (np < 0) return np;
+  affine_t A;
+  affine_init(dim, pmat, &A);
+  double meas = fabs(A.det);
+  double shape[ORC_MAXND], dref[ORC_MAXND*3], dphys[ORC_MAXND*3], tau[ST_MAXTD], dtau[ST_MAXTD];
+  for (int q = 0; q < np; q++) {
+    if (orc_h1_shape(dim, fe_order, NULL, pts + 3*q, shape, dref) < 0) return ORC_UNSUP;
+    for (int i = 0; i < nds; i++)
+      for (int d = 0; d < dim; d++) {
+        double v = 0;
+        for (int k = 0; k < dim; k++) v += dref[i*dim + k] * A.Jinv[k][d];
+        dphys[i*dim + d] = v;
+      }
+    st_lagrange(ntd_fe, tq[q], tau, dtau);
+    double fac = meas * w[q];
+    for (int j = 0; j < ntd_fe; j++) for (int i = 0; i < nds; i++)
+      for (int jp = 0; jp < ntd_fe; jp++) for (int ip = 0; ip < nds; ip++) {
+        double g = 0;
+        for (int d = 0; d < dim; d++) g += dphys[i*dim + d] * dphys[ip*dim + d];
+        double v = (c_mass * shape[i] * shape[ip] + c_stiff * g) * tau[j] * tau[jp] + c_dt * shape[i] * tau[j] * shape[ip] * dtau[jp];
+        elmat[(j*nds + i)*N + jp*nds + ip] += fac * v;
+      }
+  }
+  return np;
+}
+
+/* xfem/cutinfo.cpp:79-111 with time_order >= 0: part volumes of the space-time prism from the POS and NEG rules of order 0 in space */
+int orc_st_cutinfo_element(int dim, const double *pmat, const double *lset_st, int ntd, int time_order, double *ratio)
+{
+  static _Thread_local double pts[3*ORC_MAXPTS], w[ORC_MAXPTS], tq[ORC_MAXPTS];
+  double pv[2] = {0, 0};
+  const int order_np[2] = {POS, NEG};
+  for (int k = 0; k < 2; k++) {
+    int np = order_np[k];
+    int n = orc_st_cut_rule(dim, pmat, lset_st, ntd, np, time_order, 0, pts, tq, w, ORC_MAXPTS);
+    if (n == ORC_THROW || n == ORC_UNSUP || n == ORC_CAP) return n;
+    for (int i = 0; i < n; i++) pv[np] += w[i];
+  }
+  *ratio = pv[NEG] / (pv[NEG] + pv[POS]);
+  if (pv[NEG] > 0.0) return pv[POS] > 0.0 ? IF : NEG;
+  return POS;
+}
+
 /* IntegrateX with time_order >= 0 (cutint/python_cutint.cpp:20-72 -> CreateCutIntegrationRule, cutint/xintegration.cpp:38-58):
  * sum_e sum_q |det J_e| w_q f(x_q, t_q); mono rows {coef, ex, ey, ez, et} (et = power of the reference time tref).
  * lset_st [ntd][nvtot] global space-time vector (dof = t * ndof_space + vertex, spacetime/SpaceTimeFESpace.cpp:109-122). */
@@ -985,7 +1113,7 @@ double orc_st_integrate_mesh(int dim, int64_t ne, const int32_t *el2v, const dou
 #pragma omp parallel for schedule(static) reduction(+:sum,nptot)
   for (int64_t e = 0; e < ne; e++) {
     static _Thread_local double pts[3*ORC_MAXPTS], w[ORC_MAXPTS], tq[ORC_MAXPTS];
-    double pmat[12], ls0[4], x[3], lst[12];
+    double pmat[12], ls0[4], x[3], lst[4*ST_MAXTD];
     gather_el(dim, el2v, vert, lset_st, e, pmat, ls0, 0);
     for (int k = 0; k < ntd; k++)
       for (int v = 0; v < nv; v++) lst[k*nv + v] = lset_st[k*nvtot + el2v[e*nv + v]];

@@ -44,6 +44,8 @@ def load():
     L.orc_st_cut_rule.argtypes = [c_int, dp, dp, c_int, c_int, c_int, c_int, dp, dp, dp, c_int]
     L.orc_st_integrate_mesh.argtypes = [c_int, c_i64, ip, dp, c_i64, dp, c_int, c_int, c_int, c_int, c_int, dp, lp]
     L.orc_st_integrate_mesh.restype = c_double
+    L.orc_st_elmat_h1.argtypes = [c_int, c_int, c_int, dp, dp, c_int, c_int, c_int, c_int, c_double, c_double, c_double, dp]
+    L.orc_st_cutinfo_element.argtypes = [c_int, dp, dp, c_int, c_int, dp]
     L.orc_h1_ndof.argtypes = [c_int, c_int]
     L.orc_h1_shape.argtypes = [c_int, c_int, ip, dp, dp, dp]
     L.orc_elmat_h1.argtypes = [c_int, c_int, ip, dp, dp, c_int, c_int, c_double, c_double, dp]
@@ -143,6 +145,27 @@ def st_cut_rule(dim, pmat, lset_st, dt, order_time, order_space, impl="oracle", 
     if n < 0:
         return n, None, None, None
     return n, pts[:n].copy(), tq[:n].copy(), w[:n].copy()
+
+
+def st_elmat(dim, pmat, lset_st, fe_order, ntd_fe, dt, order_time, order_space, c_mass, c_stiff, c_dt, impl="oracle"):
+    """space-time element matrix of SpaceTimeFE(H1 order fe_order, NodalTimeFE order ntd_fe - 1): (npts, [N][N]), N = ntd_fe * nd_space"""
+    ls = _d(lset_st); pm = _d(pmat)
+    N = ntd_fe * load().orc_h1_ndof(dim, fe_order)
+    out = np.zeros((N, N))
+    if impl == "oracle":
+        n = load().orc_st_elmat_h1(dim, fe_order, ntd_fe, P(pm), P(ls), ls.shape[0], dt, order_time, order_space, c_mass, c_stiff, c_dt, P(out))
+    else:
+        from . import refload
+        n = refload.load().ref_st_elmat_h1(ET[dim], fe_order, ntd_fe, P(pm), P(ls), ls.shape[0], dt, order_time, order_space,
+                                           c_double(c_mass), c_double(c_stiff), c_double(c_dt), P(out))
+    return n, out
+
+
+def st_cutinfo_element(dim, pmat, lset_st, time_order):
+    r = c_double(0)
+    ls = _d(lset_st); pm = _d(pmat)
+    d = load().orc_st_cutinfo_element(dim, P(pm), P(ls), ls.shape[0], time_order, ctypes.byref(r))
+    return d, r.value
 
 
 def st_integrate_mesh(dim, el2v, vert, lset_st, dt, order_space, order_time, mono5=None, nthreads=0):

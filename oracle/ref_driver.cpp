@@ -661,6 +661,63 @@ int ref_st_cut_rule(int et, const double * pmat, const double * lset_st, int ntd
   } catch (...) { return -2; }
 }
 
+// space-time element matrix through the reference's own SpaceTimeFE (spacetime/SpaceTimeFE.cpp:29-113: CalcShape, CalcDShape,
+// CalcDtShape on the integration points of SpaceTimeCutIntegrationRule, which carry the reference time in Weight()) over
+// H1HighOrderFE x NodalTimeFE; the block loop  elmat += |det J| w (c_m u v + c_s grad u . grad v + c_t dt(u) v)  is this driver's.
+}  // extern "C"
+template <int D, ELEMENT_TYPE ET>
+static int st_elmat_t(int fe_order, int ntd_fe, const double * pmat, const Vector<> & lv, int ntdofs, int dt, int order_time, int order_space,
+                      double cm, double cs, double ct, double * elmat, LocalHeap & lh)
+{
+  const int nv = D + 1;
+  NodalTimeFE tfe_lset(ntdofs - 1, false, false);
+  NodalTimeFE tfe(ntd_fe - 1, false, false);
+  H1HighOrderFE<ET> sfe(fe_order);
+  SpaceTimeFE<D> stfe(&sfe, &tfe, false, 0.0);
+  Matrix<> pm(nv, D);
+  for (int i = 0; i < nv; i++) for (int d = 0; d < D; d++) pm(i,d) = pmat[i*D+d];
+  auto trafo = new (lh) FE_ElementTransformation<D,D>(ET, pm);
+  const IntegrationRule * ir = nullptr;
+  Array<double> wei;
+  tie(ir, wei) = SpaceTimeCutIntegrationRule(lv, *trafo, &tfe_lset, DOMAIN_TYPE(dt), order_time, order_space, FIND_OPTIMAL, lh);
+  const int N = stfe.GetNDof();
+  for (int i = 0; i < N*N; i++) elmat[i] = 0.0;
+  if (!ir) return -1;
+  Vector<> shape(N), dtshape(N);
+  Matrix<> dshape(N, D), dphys(N, D);
+  for (int q = 0; q < ir->Size(); q++) {
+    const IntegrationPoint & ip = (*ir)[q];
+    MappedIntegrationPoint<D,D> mip(ip, *trafo);
+    stfe.CalcShape(ip, shape);
+    stfe.CalcDShape(ip, dshape);
+    stfe.CalcDtShape(ip, dtshape);
+    dphys = dshape * mip.GetJacobianInverse();
+    const double fac = fabs(mip.GetJacobiDet()) * wei[q];
+    for (int i = 0; i < N; i++)
+      for (int j = 0; j < N; j++) {
+        double g = 0.0;
+        for (int d = 0; d < D; d++) g += dphys(i,d) * dphys(j,d);
+        elmat[i*N+j] += fac * (cm * shape(i) * shape(j) + cs * g + ct * shape(i) * dtshape(j));
+      }
+  }
+  return ir->Size();
+}
+
+extern "C" {
+int ref_st_elmat_h1(int et, int fe_order, int ntd_fe, const double * pmat, const double * lset_st, int ntdofs, int dt, int order_time,
+                    int order_space, double cm, double cs, double ct, double * elmat)
+{
+  LocalHeap & lh = GetLH(); HeapReset hr(lh);
+  try {
+    if (et != ET_TRIG && et != ET_TET) return -4;
+    const int nv = et == ET_TRIG ? 3 : 4;
+    Vector<> lv(ntdofs * nv);
+    for (int i = 0; i < ntdofs * nv; i++) lv(i) = lset_st[i];
+    if (et == ET_TRIG) return st_elmat_t<2, ET_TRIG>(fe_order, ntd_fe, pmat, lv, ntdofs, dt, order_time, order_space, cm, cs, ct, elmat, lh);
+    return st_elmat_t<3, ET_TET>(fe_order, ntd_fe, pmat, lv, ntdofs, dt, order_time, order_space, cm, cs, ct, elmat, lh);
+  } catch (...) { return -2; }
+}
+
 // xfem/cutinfo.cpp:79-111 : two order-0 rules -> part volumes -> domain + cut ratio.  returns DOMAIN_TYPE or -2
 int ref_cutinfo_element(int et, const double * pmat, const double * lset, double * ratio)
 {

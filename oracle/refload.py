@@ -42,6 +42,8 @@ def load():
     L.ref_cut_rule.argtypes = [c_int, dp, dp, c_int, c_int, dp, dp, c_int]
     L.ref_cutinfo_element.argtypes = [c_int, dp, dp, dp]
     L.ref_st_cut_rule.argtypes = [c_int, dp, dp, c_int, c_int, c_int, c_int, dp, dp, dp, c_int]
+    if hasattr(L, "ref_st_elmat_h1"):
+        L.ref_st_elmat_h1.argtypes = [c_int, c_int, c_int, dp, dp, c_int, c_int, c_int, c_int, c_double, c_double, c_double, dp]
     L.ref_h1_ndof.argtypes = [c_int, c_int]
     L.ref_h1_shape.argtypes = [c_int, c_int, ip, dp, dp, dp]
     L.ref_elmat_h1.argtypes = [c_int, c_int, ip, dp, dp, c_int, c_int, c_double, c_double, dp]

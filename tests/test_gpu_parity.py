@@ -633,6 +633,112 @@ def test_spacetime_rule_vs_oracle(X, dim, tord):
                                        cf=1.0 + 0.5 * ngs.x * tref ** 2 - 0.25 * ngs.y ** 2 * tref, mesh=mesh, order=os_, time_order=ot)
 
 
+def _st_setup(X, dim, tord, nx2=6, nx3=3, wobble=0.0):
+    ngs, xf = X.ngs, X.xfem
+    mesh = ngs.Mesh(X.meshes.MakeStructured2DMesh(nx2) if dim == 2 else X.meshes.MakeStructured3DMesh(nx3))
+    fes = xf.SpaceTimeFESpace(ngs.H1(mesh, order=1), xf.ScalarTimeFE(tord))
+    gf = ngs.GridFunction(fes)
+    c = (0.45, 0.5, 0.55)[:dim]
+
+    def lset(*a):
+        *xs, t = a
+        r2 = sum((xs[d] - c[d] - (0.25 * t if d == 0 else 0.1 * t * t)) ** 2 for d in range(dim))
+        return torch.sqrt(r2) - 0.3 + wobble * np.sin(9.0 * t)
+    xf.SpaceTimeInterpolateToP1(lset, None, gf)
+    return mesh, fes, gf
+
+
+@pytest.mark.parametrize("dim", [2, 3])
+@pytest.mark.parametrize("tord", [3, 4, 5])
+def test_spacetime_rule_time_orders_above_two(X, dim, tord):
+    """f-3: time elements of order 3..5 (Gauss-Lobatto nodes, subdivision + secant / bisection roots, cutint/spacetimecutrule.cpp:46-95)
+    against the oracle, which is pinned against the compiled reference at these orders (tests/test_oracle_spacetime.py)"""
+    from oracle import orc
+    from ngsxfem_b200 import spacetime
+    ngs, xf = X.ngs, X.xfem
+    mesh, fes, gf = _st_setup(X, dim, tord, wobble=0.04)                # the wobble gives vertex traces with several roots
+    el2v, vert = mesh.el2v.cpu().numpy(), mesh.vert.cpu().numpy()
+    ls = gf.vec.cpu().numpy().reshape(tord + 1, mesh.nv)
+    tref = xf.ReferenceTimeVariable()
+    nmulti = 0
+    for dt in (NEG, POS, IF):
+        for os_, ot in ((0, 0), (2, 3)):
+            npts, offs, pts, tq, w = (a.cpu().numpy() for a in spacetime.cut_rule(gf, mesh, dt, os_, ot))
+            for e in range(mesh.ne):
+                n, p_o, t_o, w_o = orc.st_cut_rule(dim, vert[el2v[e]], ls[:, el2v[e]], dt, ot, os_)
+                assert max(n, 0) == npts[e], (e, dt, os_, ot)
+                if n > 0:
+                    sl = slice(offs[e], offs[e] + n)
+                    nmulti += len(np.unique(np.round(t_o, 12))) > (ot // 2 + 1)
+                    assert np.abs(pts[sl] - p_o).max() < 1e-11 and np.abs(tq[sl] - t_o).max() < 1e-13
+                    assert np.abs(w[sl] - w_o).max() <= 1e-11 * np.abs(w_o).max()
+            mono = [[1.0, 0, 0, 0, 0], [0.5, 1, 0, 0, 2]]
+            ref, _ = orc.st_integrate_mesh(dim, el2v, vert, ls, dt, os_, ot, mono)
+            got = xf.Integrate(levelset_domain={"levelset": gf, "domain_type": dt}, cf=1.0 + 0.5 * ngs.x * tref ** 2, mesh=mesh, order=os_, time_order=ot)
+            assert abs(got - ref) <= 1e-11 * max(abs(ref), 1e-3)
+    assert nmulti > 0                                                      # some elements were split in time
+
+
+@pytest.mark.parametrize("dim,fo,tfe,tls", [(2, 1, 1, 1), (2, 2, 1, 2), (2, 1, 2, 2), (3, 1, 1, 1), (3, 2, 1, 1), (3, 1, 2, 3), (2, 2, 2, 1)])
+def test_spacetime_element_matrices_and_operator(X, dim, fo, tfe, tls):
+    """f-3: SpaceTimeFE element matrices (H1 order fo x NodalTimeFE order tfe; mass + stiffness + dt(u) v) on the space-time cut rule of a
+    level set of time order tls, against the oracle (pinned against the compiled SpaceTimeFE), and the assembled operator"""
+    from oracle import orc
+    from ngsxfem_b200 import spacetime
+    ngs, xf = X.ngs, X.xfem
+    mesh, _, gf = _st_setup(X, dim, tls, nx2=5, nx3=2)
+    fes = xf.SpaceTimeFESpace(ngs.H1(mesh, order=fo), xf.ScalarTimeFE(tfe))
+    el2v, vert = mesh.el2v.cpu().numpy(), mesh.vert.cpu().numpy()
+    ls = gf.vec.cpu().numpy().reshape(tls + 1, mesh.nv)
+    N = fes.nd
+    for dt in (NEG, POS, IF):
+        got = spacetime.elmats(fes, gf, dt, 1.3, 0.7, -0.9).cpu().numpy()
+        ref = np.zeros_like(got)
+        for e in range(mesh.ne):
+            _, ref[e] = orc.st_elmat(dim, vert[el2v[e]], ls[:, el2v[e]], fo, tfe + 1, dt, 2 * tfe, 2 * fo, 1.3, 0.7, -0.9)
+        assert np.abs(ref).max() > 0
+        assert relerr_rows(got, ref) <= RTOL
+        if N in (3, 4, 5, 6, 8, 9, 10, 12, 14, 20):
+            op = spacetime.SpaceTimeOperator(fes, gf, dt, 1.3, 0.7, -0.9).Assemble()
+            first = op.mat.vals.clone()
+            op.mat.vals.fill_(float("nan"))
+            op.Assemble()
+            assert torch.equal(first, op.mat.vals)                                  # bitwise reproducible
+            dense = np.zeros((fes.ndof, fes.ndof))
+            tab = fes.el2dof.cpu().numpy()
+            for e in range(mesh.ne):
+                dense[np.ix_(tab[e], tab[e])] += ref[e]
+            A = op.mat.to_scipy().toarray()
+            assert np.abs(A - dense).max() <= 1e-12 * np.abs(dense).max()
+    els = torch.arange(0, mesh.ne, 3, dtype=torch.int32, device="cuda")
+    sub = spacetime.elmats(fes, gf, NEG, 1.0, 0.0, 0.0, els=els)
+    assert torch.equal(sub, spacetime.elmats(fes, gf, NEG, 1.0, 0.0, 0.0)[els.long()])
+
+
+@pytest.mark.parametrize("dim", [2, 3])
+def test_spacetime_cutinfo(X, dim):
+    """f-3: CutInfo.Update(levelset, time_order) -- element classes of the space-time prisms (xfem/cutinfo.cpp:79-111 with the
+    space-time rules) against the oracle"""
+    from oracle import orc
+    xf = X.xfem
+    for tord in (1, 2, 3):
+        mesh, fes, gf = _st_setup(X, dim, tord)
+        el2v, vert = mesh.el2v.cpu().numpy(), mesh.vert.cpu().numpy()
+        ls = gf.vec.cpu().numpy().reshape(tord + 1, mesh.nv)
+        ci = xf.CutInfo(mesh, gf, time_order=2)
+        dom, ratio = ci.dom.cpu().numpy(), ci.ratio.cpu().numpy()
+        for e in range(mesh.ne):
+            d, r = orc.st_cutinfo_element(dim, vert[el2v[e]], ls[:, el2v[e]], 2)
+            assert d == dom[e] and abs(r - ratio[e]) < 1e-13
+        assert {POS, IF} <= set(dom.tolist()) and (dim == 3 or NEG in set(dom.tolist()))    # the coarse 3D mesh has no prism inside for the whole slab
+        nif = int((dom == IF).sum())
+        assert ci.GetElementsOfType(xf.IF).NumSet() == nif and ci.GetElementsOfType(xf.HASNEG).NumSet() == int((dom != POS).sum())
+        # an element that is cut at SOME time of the slab is IF: at least as many as at the start time
+        gf0 = X.ngs.GridFunction(X.ngs.H1(mesh, order=1))
+        gf0.vec.copy_(gf.vec[:mesh.nv])
+        assert nif >= xf.CutInfo(mesh, gf0).GetElementsOfType(xf.IF).NumSet()
+
+
 def test_spacetime_reference_kats_and_scale(X):
     """tests/pytests/test_spacetimecutrule.py:12-68 on the GPU + config 5 (2D+t moving circle, ~2 M triangles, order 2 x 2):
     NEG + POS = |Omega| x 1, space-time volume of the moving disc, interface measure integrated in time"""
@@ -653,7 +759,7 @@ def test_spacetime_reference_kats_and_scale(X):
         val = xf.Integrate(levelset_domain={"levelset": gf, "domain_type": dt}, cf=1.0, mesh=mesh, order=0, time_order=0)
         assert abs(val - ref) < 5e-15
     with pytest.raises(X.lib.NgsxError):
-        xf.ScalarTimeFE(3)
+        xf.ScalarTimeFE(6)
     # config 5
     nx = 1000
     mesh = ngs.Mesh(X.meshes.MakeStructured2DMesh(nx, device="cuda"))

@@ -23,6 +23,9 @@ def main():
     gf = ngs.GridFunction(xf.SpaceTimeFESpace(ngs.H1(mesh, order=1), xf.ScalarTimeFE(2)))
     xf.SpaceTimeInterpolateToP1(lambda xx, yy, t: torch.sqrt((xx - 0.35 - 0.3 * t) ** 2 + (yy - 0.5) ** 2) - 0.25, None, gf)
     ev = lambda: torch.cuda.Event(enable_timing=True)
+    import bench
+    clocks = bench.ClockSampler(0)
+    clocks.start()
 
     def timed(fn):
         for _ in range(3):
@@ -45,6 +48,16 @@ def main():
         out["ms"][f"rule count+scan+fill({name})"] = t_rule
         out[f"points_{name}"] = int(rule[2].shape[0])
         out[f"value_{name}"] = float(val.item())
+    # f-3 remainder: space-time CutInfo, SpaceTimeFE element matrices (P1 x nodal order 1: 6 x 6 blocks) and the assembled operator
+    out["ms"]["CutInfo.Update(time_order=2)"], _ = timed(lambda: spacetime.classify(gf, mesh, 2))
+    fes = xf.SpaceTimeFESpace(ngs.H1(mesh, order=1), xf.ScalarTimeFE(1))
+    blocks = torch.empty((mesh.ne, fes.nd, fes.nd), dtype=torch.float64, device="cuda:0")
+    out["ms"]["SpaceTimeFE element matrices (NEG, mass + stiffness + dt)"], _ = timed(lambda: spacetime.elmats(fes, gf, xf.NEG, 1.0, 1.0, 1.0, out=blocks))
+    del blocks
+    op = spacetime.SpaceTimeOperator(fes, gf, xf.NEG, 1.0, 1.0, 1.0)
+    out["ms"]["SpaceTimeOperator.Assemble (blocks + row gather)"], _ = timed(lambda: op.Assemble())
+    out["nnz_spacetime_operator"] = op.mat.nnz
+    out["elements_per_s_st_assemble"] = mesh.ne / (out["ms"]["SpaceTimeOperator.Assemble (blocks + row gather)"] * 1e-3)
     out["elements_per_s_integrate_NEG"] = mesh.ne / (out["ms"]["Integrate(NEG)"] * 1e-3)
     out["points_per_s_fill_NEG"] = out["points_NEG"] / (out["ms"]["rule count+scan+fill(NEG)"] * 1e-3)
     try:
@@ -61,6 +74,7 @@ def main():
                                     "sample": f"{len(sample)} elements through oracle/_ref (spacetimecutrule.cpp) incl. ctypes call overhead"}
     except Exception as exc:
         out["cpu_reference"] = {"error": str(exc)[:100]}
+    out["clocks"] = clocks.stop()
     print(json.dumps(out))
 
 
