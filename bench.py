@@ -385,6 +385,22 @@ def run_b200(args):
                         "step": statistics.mean(e[0].elapsed_time(e[5]) for e in rec_s),
                         "kernel_ms": None if ks is None else {"k_geom": ks[0], "k_cutmat": ks[1], "k_rows": ks[2]}}
 
+    # the timed Integrate calls use cf = 1 (BASELINE config), which the kernels serve without a point loop (measure x sum of weights);
+    # beside it: the general integrand path (polynomial evaluated at every rule point), untimed region, N = 1 only
+    if serial_break is not None and pworld == 1:
+        from ngsxfem_b200.ngs import x as cx, y as cy, z as cz
+        cf_gen = 1.0 + cx * cy + 0.5 * cz * cz
+        for name, dt_ in (("integrate_general_IF", xfem.IF), ("integrate_general_NEG", xfem.NEG)):
+            for _ in range(3):
+                xfem.IntegrateX(lsetp1, mesh_int, cf=cf_gen, order=4, domain_type=dt_, sync=False)
+            g0, g1 = ev(), ev()
+            g0.record()
+            for _ in range(5):
+                xfem.IntegrateX(lsetp1, mesh_int, cf=cf_gen, order=4, domain_type=dt_, sync=False)
+            g1.record()
+            torch.cuda.synchronize()
+            serial_break[name] = g0.elapsed_time(g1) / 5
+
     # ---- e2e: level set from pinned host memory every step, CSR values + integrals back to the host ----------------
     h_lset = lsetp1.vec.cpu().pin_memory()
     # N > 1: the rows a rank owns are a few runs of the CSR (vertex dofs of its slab, then its edge dofs): they are downloaded as

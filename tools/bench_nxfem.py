@@ -50,6 +50,9 @@ def main():
     torch.cuda.synchronize()
     setup_s = time.time() - t0
     ev = lambda: torch.cuda.Event(enable_timing=True)
+    import bench
+    clocks = bench.ClockSampler(0)
+    clocks.start()
     for _ in range(3):
         a.Assemble()
     torch.cuda.synchronize()
@@ -68,6 +71,7 @@ def main():
            "xfespace_update_s": round(t_xfes, 3), "first_assemble_s(symbolic+numeric)": round(setup_s, 2),
            "assemble_ms": ms, "elements_per_s": mesh.ne / (ms * 1e-3),
            "asymmetry_rel": float(abs(sym).max() / abs(a.mat.to_scipy()).max())}
+    out["clocks"] = clocks.stop()
     print(json.dumps(out))
 
 

@@ -36,6 +36,9 @@ def main():
     torch.cuda.synchronize()
     setup_s = time.time() - t0
     ev = lambda: torch.cuda.Event(enable_timing=True)
+    import bench
+    clocks = bench.ClockSampler(0)
+    clocks.start()
     for _ in range(3):
         a.Assemble()
     torch.cuda.synchronize()
@@ -53,6 +56,7 @@ def main():
            "ne": mesh.ne, "if_elements": nif, "ghost_facets": npatch, "nnz": int(a.mat.nnz),
            "first_assemble_s(symbolic+numeric)": round(setup_s, 2), "assemble_ms": ms,
            "if_elements_per_s": nif / (ms * 1e-3), "patches_per_s": npatch / (ms * 1e-3)}
+    out["clocks"] = clocks.stop()
     print(json.dumps(out))
 
 
