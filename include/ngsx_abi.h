@@ -154,6 +154,9 @@ int ngsx_elvec_h1(const ngsx_mesh *mesh, const double *lset_v, int fe_order, int
 typedef struct ngsx_graph ngsx_graph;   /* opaque, host object owning temporary device buffers */
 int ngsx_csr_graph_create(int64_t ndof, ngsx_graph **out);
 /* add the couplings of a dof table [n][nd] (element dofs of marked elements, or the merged dofs of facet patches) */
+/* symmetric storage (BilinearForm(symmetric=True): SparseMatrixSymmetric keeps the lower triangle, AddElementMatrixSymmetric,
+ * NGS/linalg/sparsematrix_impl.hpp:605-690): call before the first add_table; the graph then keeps the couplings col <= row only */
+int ngsx_csr_graph_set_lower(ngsx_graph *g, int on);
 int ngsx_csr_graph_add_table(ngsx_graph *g, int64_t n, int32_t nd, const int32_t *table, void *stream);
 /* sort + unique; synchronises the stream; returns nnz */
 int ngsx_csr_graph_finalize(ngsx_graph *g, int64_t *h_nnz, void *stream);
@@ -195,6 +198,11 @@ int ngsx_rowplan_create(int64_t nlist, int32_t nd, const int32_t *table, int64_t
  * the first listed element that touches it (ngsxfem_b200/partition.py) -- contiguous dof ranges would hand every rank all
  * vertex rows of an H1 space numbered "vertices, then edges".  The window of a tile may span rows of other owners; their
  * entries in the caller's (rank-local) value array are scratch. */
+/* row plan over a lower-triangle pattern made with ngsx_csr_graph_set_lower: the local columns of a pair that lie above its row have
+ * no slot and are skipped by the gather; every stored value is still written once, in plan order (bitwise the lower triangle of the
+ * unsymmetric assembly).  Served by ngsx_assemble_csr_rows_h1 (rows of < 255 entries); the block gathers reject such plans. */
+int ngsx_rowplan_create_lower(int64_t nlist, int32_t nd, const int32_t *table, int64_t ndof, const int64_t *rowptr, const int32_t *colidx,
+                              int64_t row_lo, int64_t row_hi, ngsx_rowplan **out, void *stream);
 int ngsx_rowplan_create_owned(int64_t nlist, int32_t nd, const int32_t *table, int64_t ndof, const int64_t *rowptr, const int32_t *colidx,
                               const int32_t *row_owner, int32_t me, ngsx_rowplan **out, void *stream);
 /* h_info[0..5] = {non-empty rows, (row, element) pairs, CSR entries covered by the plan's rows, longest row, first covered CSR

@@ -65,6 +65,7 @@ SIGNATURES = {
                               c_void_p, c_void_p, c_void_p]),
     "ngsx_gather_vec": (c_int, [c_i64, c_void_p, c_void_p, c_void_p, ctypes.c_double, c_int, c_void_p, c_void_p]),
     "ngsx_csr_graph_create": (c_int, [c_i64, ctypes.POINTER(c_void_p)]),
+    "ngsx_csr_graph_set_lower": (c_int, [c_void_p, c_int]),
     "ngsx_csr_graph_add_table": (c_int, [c_void_p, c_i64, c_i32, c_void_p, c_void_p]),
     "ngsx_csr_graph_finalize": (c_int, [c_void_p, ctypes.POINTER(c_i64), c_void_p]),
     "ngsx_csr_graph_export": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p]),
@@ -76,6 +77,7 @@ SIGNATURES = {
     "ngsx_assemble_vec_h1": (c_int, [ctypes.POINTER(Mesh), c_void_p, c_int, c_int, c_int, ctypes.POINTER(Poly), c_i64, c_void_p,
                                      c_void_p, c_i32, c_void_p, c_i32, c_void_p, c_void_p]),
     "ngsx_rowplan_create": (c_int, [c_i64, c_i32, c_void_p, c_i64, c_void_p, c_void_p, c_i64, c_i64, ctypes.POINTER(c_void_p), c_void_p]),
+    "ngsx_rowplan_create_lower": (c_int, [c_i64, c_i32, c_void_p, c_i64, c_void_p, c_void_p, c_i64, c_i64, ctypes.POINTER(c_void_p), c_void_p]),
     "ngsx_rowplan_create_owned": (c_int, [c_i64, c_i32, c_void_p, c_i64, c_void_p, c_void_p, c_void_p, c_i32, ctypes.POINTER(c_void_p), c_void_p]),
     "ngsx_rowplan_info": (c_int, [c_void_p, ctypes.POINTER(c_i64)]),
     "ngsx_rowplan_destroy": (c_int, [c_void_p]),
@@ -144,6 +146,8 @@ def load():
     lib.ngsx_debug_set_fast_path.restype = None
     lib.ngsx_debug_set_order3_fma.argtypes = [c_int]
     lib.ngsx_debug_set_order3_fma.restype = None
+    lib.ngsx_debug_set_elvec_warp.argtypes = [c_int]
+    lib.ngsx_debug_set_elvec_warp.restype = None
     lib.ngsx_debug_set_deformed_warp.argtypes = [c_int]
     lib.ngsx_debug_set_deformed_warp.restype = None
     lib.ngsx_debug_set_timing.argtypes = [c_int]

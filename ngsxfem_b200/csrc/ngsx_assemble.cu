@@ -883,6 +883,152 @@ __global__ void __launch_bounds__(WARPS * 32) k_elvec(ElvecArgs A, int64_t first
   }
 }
 
+// ---------------------------------------------------------------------------------------------------------------
+// element vectors, ONE THREAD PER LIST ENTRY (orders 1-2, dense sink): the warp-per-element kernel above keeps ~10 of 32 lanes
+// busy on an uncut element (3.7 ms for the 942 504 HASNEG P2 tets of a 4.98 M-tet mesh).  Two passes like the deformed kernels:
+// pass 1 integrates the uncut entries of the domain (ND accumulators in registers, rule points as shared-memory broadcasts) and
+// records the cut ones (integer slot from an atomic counter; every vector is written at its own entry, so the order of the list
+// never reaches a value); pass 2 walks the recorded entries through the sub-simplex rules.
+// ---------------------------------------------------------------------------------------------------------------
+struct ElvecTArgs {
+  ElvecArgs E;
+  int32_t *work; int32_t *work_count;
+};
+
+template <int DIM>
+__device__ __forceinline__ double poly_at(const PolyDev2 &f, const double *lam, const double (*p)[DIM]) {
+  double x[3] = {0.0, 0.0, 0.0};
+#pragma unroll
+  for (int d = 0; d < DIM; d++) {
+    double v = 0.0;
+#pragma unroll
+    for (int kk = 0; kk <= DIM; kk++) v += lam[kk] * p[kk][d];
+    x[d] = v;
+  }
+  double fx = 0.0;
+  for (int m = 0; m < f.n; m++) fx += f.c[m] * ipow(x[0], f.ex[m][0]) * ipow(x[1], f.ex[m][1]) * ipow(x[2], f.ex[m][2]);
+  return fx;
+}
+
+template <int DIM, int ORDER, bool CUTPASS>
+__global__ void __launch_bounds__(128) k_elvec_t(ElvecTArgs T, int64_t nlist) {
+  constexpr int ND = H1<DIM, ORDER>::ND;
+  const ElvecArgs &A = T.E;
+  extern __shared__ __align__(16) unsigned char smem_raw[];
+  double4 *srule_vol = reinterpret_cast<double4 *>(smem_raw);
+  double4 *srule_if = srule_vol + A.nr_vol;
+  CutEntry *lut = reinterpret_cast<CutEntry *>(srule_if + A.nr_if);
+  for (int i = threadIdx.x; i < A.nr_vol; i += blockDim.x) srule_vol[i] = A.rule_vol[i];
+  for (int i = threadIdx.x; i < A.nr_if; i += blockDim.x) srule_if[i] = A.rule_if[i];
+  if (threadIdx.x < 16) lut[threadIdx.x] = A.tab->e[DIM - 2][A.dt][threadIdx.x];
+  __syncthreads();
+  const int64_t w = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  int64_t k = w;
+  if constexpr (CUTPASS) {
+    if (w >= (int64_t)*T.work_count) return;
+    k = T.work[w];
+  } else if (w >= nlist) return;
+  const int64_t e = A.els ? A.els[k] : k;
+  double ls[4], p[DIM + 1][DIM];
+  load_el<DIM>(A.M, A.lset, e, ls, p);
+  int mask;
+  const int dom = sign_test<DIM>(ls, mask);
+  double acc[ND];
+#pragma unroll
+  for (int i = 0; i < ND; i++) acc[i] = 0.0;
+  int np_used = 0;
+  if constexpr (!CUTPASS) {
+    if (dom == IF) {
+      T.work[atomicAdd(T.work_count, 1)] = (int32_t)k;
+      return;
+    }
+    if (dom == A.dt) {
+      np_used = A.nr_vol;
+      for (int q = 0; q < A.nr_vol; q++) {
+        const double4 r = srule_vol[q];
+        double lam[4] = {r.x, r.y, r.z, 0.0};
+        double last = 1.0;
+#pragma unroll
+        for (int kk = 0; kk < DIM; kk++) last -= lam[kk];
+        lam[DIM] = last;
+        const double fw = r.w * poly_at<DIM>(A.f, lam, p);
+#pragma unroll
+        for (int i = 0; i < ND; i++) acc[i] += fw * h1_shape<DIM, ORDER>(i, lam);
+      }
+    }
+  } else {
+    ElGeom<DIM> G;
+    element_geometry<DIM>(p, G);
+    double scale = 1.0;
+    if (A.dt == IF) {
+      double gl[DIM + 1][DIM];
+      bary_gradients<DIM>(G, gl);
+      double g2 = 0.0, r2 = 0.0;
+#pragma unroll
+      for (int d = 0; d < DIM; d++) {
+        double v = 0.0;
+#pragma unroll
+        for (int kk = 0; kk <= DIM; kk++) v += ls[kk] * gl[kk][d];
+        g2 += v * v;
+      }
+#pragma unroll
+      for (int kk = 0; kk < DIM; kk++) { double v = ls[kk] - ls[DIM]; r2 += v * v; }
+      scale = sqrt(g2) / sqrt(r2);
+    }
+    const CutEntry E = lut[mask];
+    const double4 *rule = A.dt == IF ? srule_if : srule_vol;
+    const int nr = A.dt == IF ? A.nr_if : A.nr_vol;
+    np_used = E.ns * nr;
+    for (int s = 0; s < E.ns; s++) {
+      double P[4][3];
+      for (int v = 0; v < E.npt; v++) coded_point<DIM>(E.v[s][v], ls, P[v]);
+      const double sfac = simplex_factor(E.npt, P) * scale;
+      for (int q = 0; q < nr; q++) {
+        const double4 r = rule[q];
+        double xi[3];
+        simplex_point(E.npt, P, r, xi);
+        double lam[4] = {xi[0], xi[1], xi[2], 0.0};
+        double last = 1.0;
+#pragma unroll
+        for (int kk = 0; kk < DIM; kk++) last -= lam[kk];
+        lam[DIM] = last;
+        const double fw = (r.w * sfac) * poly_at<DIM>(A.f, lam, p);
+#pragma unroll
+        for (int i = 0; i < ND; i++) acc[i] += fw * h1_shape<DIM, ORDER>(i, lam);
+      }
+    }
+  }
+  double meas = 0.0;
+  if (np_used) {
+    ElGeom<DIM> G;
+    element_geometry<DIM>(p, G);
+    meas = fabs(G.det);
+  }
+  double *o = A.elvecs + k * ND;
+#pragma unroll
+  for (int i = 0; i < ND; i++) o[i] = meas * acc[i];
+  if (A.npts) A.npts[k] = np_used;
+}
+
+template <int DIM, int ORDER>
+static int launch_elvec_t(const ElvecArgs &A, int64_t nlist, cudaStream_t st) {
+  if (nlist >= (int64_t)INT32_MAX) { set_error("elvec_h1: more than 2^31 - 1 list entries"); return NGSX_ERR_ARG; }
+  int32_t *work = nullptr;
+  NGSX_CUDA(cudaMallocAsync(&work, (nlist + 1) * sizeof(int32_t), st));
+  ElvecTArgs T{A, work + 1, work};
+  cudaError_t e0 = cudaMemsetAsync(work, 0, sizeof(int32_t), st);
+  const size_t smem = (size_t)(A.nr_vol + A.nr_if) * 32 + 16 * sizeof(CutEntry);
+  const unsigned nb = (unsigned)((nlist + 127) / 128);
+  k_elvec_t<DIM, ORDER, false><<<nb, 128, smem, st>>>(T, nlist);
+  k_elvec_t<DIM, ORDER, true><<<nb, 128, smem, st>>>(T, nlist);
+  g_launches.fetch_add(2, std::memory_order_relaxed);
+  cudaError_t e1 = cudaGetLastError();
+  cudaFreeAsync(work, st);
+  NGSX_CUDA(e0);
+  NGSX_CUDA(e1);
+  return NGSX_OK;
+}
+
 // slot map: one thread per (list entry, i, j): binary search of the sorted CSR row
 __global__ void __launch_bounds__(256) k_slot_map(int64_t n, int nd, const int32_t *__restrict__ table, const int64_t *__restrict__ rowptr,
                                                  const int32_t *__restrict__ colidx, int32_t *__restrict__ slots) {
@@ -931,6 +1077,7 @@ static int fill_common(const ngsx_mesh *mesh, const double *lset_v, int fe_order
   return NGSX_OK;
 }
 
+static int g_elvec_warp = 0;      // debug: dense element vectors through the warp-per-element kernel k_elvec (A/B and parity)
 static int g_order3_fma = 0;      // debug: order 3 through the first-generation FMA kernel k_elmat<DIM,3> (A/B and parity)
 
 template <int DIM, int SINK>
@@ -1547,6 +1694,7 @@ extern "C" {
 // test hook: 0 disables the constant-rule path so both paths can be compared on the GPU
 void ngsx_debug_set_fast_path(int on) { g_use_fast = on; }
 void ngsx_debug_set_order3_fma(int on) { g_order3_fma = on; }
+void ngsx_debug_set_elvec_warp(int on) { g_elvec_warp = on; }
 
 // measurement hook: when on, ngsx_assemble_csr_rows_h1 records events around its kernels (a ring of 64 event sets, so the
 // caller need not synchronise every step); ngsx_debug_get_timing waits for the last call and returns the mean over the calls
@@ -1702,6 +1850,13 @@ int ngsx_elvec_h1(const ngsx_mesh *mesh, const double *lset_v, int fe_order, int
   A.M = *mesh; A.lset = lset_v; A.tab = dd->cut_table; A.dt = dt;
   A.rule_vol = rv; A.nr_vol = nv; A.rule_if = ri; A.nr_if = ni;
   A.els = els; A.group = 1; A.elvecs = elvecs; A.npts = npts;
+  if (!g_elvec_warp)                                       // orders 1-2: thread per entry, two passes (order 3 stays on the warp kernel)
+    switch (mesh->dim * 10 + fe_order) {
+      case 21: return launch_elvec_t<2, 1>(A, nlist, as_stream(stream));
+      case 22: return launch_elvec_t<2, 2>(A, nlist, as_stream(stream));
+      case 31: return launch_elvec_t<3, 1>(A, nlist, as_stream(stream));
+      case 32: return launch_elvec_t<3, 2>(A, nlist, as_stream(stream));
+    }
   return dispatch_elvec<0>(A, fe_order, dd->sm_count, 1, nullptr, nlist, as_stream(stream));
 }
 

@@ -11,11 +11,12 @@ struct ngsx_graph {
   std::vector<std::pair<uint64_t *, int64_t>> chunks;   // device key buffers
   uint64_t *keys = nullptr;                             // sorted unique keys after finalize
   int64_t nnz = -1;
+  int lower = 0;                                        // keep the couplings col <= row only (symmetric storage)
 };
 
 namespace ngsx {
 
-__global__ void __launch_bounds__(256) k_make_keys(int64_t n, int nd, const int32_t *__restrict__ table, uint64_t *__restrict__ keys) {
+__global__ void __launch_bounds__(256) k_make_keys(int64_t n, int nd, const int32_t *__restrict__ table, uint64_t *__restrict__ keys, int lower) {
   int64_t t = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
   int ne = nd * nd;
   if (t >= n * ne) return;
@@ -23,7 +24,7 @@ __global__ void __launch_bounds__(256) k_make_keys(int64_t n, int nd, const int3
   int idx = (int)(t % ne);
   int32_t r = table[k * nd + idx / nd], c = table[k * nd + idx % nd];
   // negative dof numbers (unused / padded entries) are parked on an out-of-range key and dropped at finalize
-  keys[t] = (r < 0 || c < 0) ? ~0ULL : (((uint64_t)(uint32_t)r << 32) | (uint32_t)c);
+  keys[t] = (r < 0 || c < 0 || (lower && c > r)) ? ~0ULL : (((uint64_t)(uint32_t)r << 32) | (uint32_t)c);
 }
 
 __global__ void __launch_bounds__(256) k_export_cols(int64_t nnz, const uint64_t *__restrict__ keys, int32_t *__restrict__ colidx) {
@@ -56,13 +57,18 @@ int ngsx_csr_graph_create(int64_t ndof, ngsx_graph **out) {
   return NGSX_OK;
 }
 
+int ngsx_csr_graph_set_lower(ngsx_graph *g, int on) {
+  NGSX_REQUIRE(g && g->chunks.empty() && g->nnz < 0, "csr_graph_set_lower: call before the first add_table");
+  g->lower = on ? 1 : 0;
+  return NGSX_OK;
+}
 int ngsx_csr_graph_add_table(ngsx_graph *g, int64_t n, int32_t nd, const int32_t *table, void *stream) {
   NGSX_REQUIRE(g && n >= 0 && nd > 0 && (n == 0 || table), "csr_graph_add_table: bad arguments");
   if (n == 0) return NGSX_OK;
   int64_t cnt = n * nd * nd;
   uint64_t *keys = nullptr;
   NGSX_CUDA(cudaMalloc(&keys, cnt * sizeof(uint64_t)));
-  k_make_keys<<<(unsigned)((cnt + 255) / 256), 256, 0, as_stream(stream)>>>(n, nd, table, keys);
+  k_make_keys<<<(unsigned)((cnt + 255) / 256), 256, 0, as_stream(stream)>>>(n, nd, table, keys, g->lower);
   g->chunks.emplace_back(keys, cnt);
   NGSX_LAUNCH_CHECK();
   return NGSX_OK;

@@ -82,7 +82,7 @@ __global__ void __launch_bounds__(128) k_plan_desc(int64_t npairs, int64_t nrows
                                                   const int64_t *__restrict__ tile_d0, const int64_t *__restrict__ tile_so,
                                                   const int32_t *__restrict__ stepoffs, const int32_t *__restrict__ table,
                                                   const int64_t *__restrict__ rowptr, const int32_t *__restrict__ colidx,
-                                                  uint8_t *__restrict__ desc, int *__restrict__ bad) {
+                                                  uint8_t *__restrict__ desc, int *__restrict__ bad, int lower) {
   const int64_t pp = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (pp >= npairs) return;
   int64_t lo = 0, hi = nrows;                                   // plan row of the pair: last q with pairptr[q] <= pp
@@ -111,8 +111,11 @@ __global__ void __launch_bounds__(128) k_plan_desc(int64_t npairs, int64_t nrows
       if (colidx[mid] < col) a = mid + 1; else b = mid;
     }
     int64_t pos = a - rs0;
-    if (b < rs0 || colidx[a] != col) { atomicOr(bad, 1); pos = 0; }
-    if (pos >= MAXROW) { atomicOr(bad, 2); pos = 0; }
+    if (lower && col > r) pos = POS_SKIP;                       // symmetric storage: the row keeps its columns <= row only
+    else {
+      if (b < rs0 || colidx[a] != col) { atomicOr(bad, 1); pos = 0; }
+      if (pos >= (lower ? POS_SKIP : MAXROW)) { atomicOr(bad, 2); pos = 0; }
+    }
     d[6 + j] = (uint8_t)pos;
   }
 }
@@ -349,18 +352,19 @@ __device__ __forceinline__ uint32_t load_geo(const RowArgs &A, uint32_t w0, doub
 
 // Row of a quadrature (cut) element: nd doubles of the cut buffer added to the window.  Out of line on purpose -- inlined, its
 // loads take the scoreboard of the next step's descriptor / geometry loads and every step of the fast path waits for those.
-template <int ND>
+template <int ND, bool LOWER>
 __device__ __noinline__ void cut_row_add(const double *__restrict__ cm, double *accrow, uint4 d) {
   double v[ND];
   int pos[ND];
   row_values_cut<ND>(cm, v);
   desc_positions<ND, 0>(d, pos);
 #pragma unroll
-  for (int j = 0; j < ND; j++) accrow[pos[j]] += v[j];
+  for (int j = 0; j < ND; j++)
+    if (!LOWER || pos[j] != POS_SKIP) accrow[pos[j]] += v[j];
 }
 
 // one (row, element) pair with a constant rule: closed-form row added at the pair's column positions of the window
-template <int DIM, int ORDER>
+template <int DIM, int ORDER, bool LOWER>
 __device__ __forceinline__ void row_step(const RowArgs &A, double *accrow, const uint4 &d, const double *ga, const double *gb) {
   constexpr int ND = H1<DIM, ORDER>::ND;
   const int i = (int)(d.x >> DESC_KBITS);
@@ -378,6 +382,12 @@ __device__ __forceinline__ void row_step(const RowArgs &A, double *accrow, const
   desc_positions<ND, 0>(d, pos);
   // the nd columns of an element are distinct: read a batch, add, write it (no serialised read-modify-write chain; two
   // batches keep the live registers under the 128 of four CTAs per SM)
+  if constexpr (LOWER) {                                          // symmetric storage: columns above the row have no slot
+#pragma unroll
+    for (int j = 0; j < ND; j++)
+      if (pos[j] != POS_SKIP) accrow[pos[j]] += v[j];
+    return;
+  }
   constexpr int HB = (ND + 1) / 2;
   double w[HB];
 #pragma unroll
@@ -434,8 +444,8 @@ __device__ __forceinline__ void header_wait() {
       const bool cut = coded && payload != 0u;                                             \
       const double *cm = A.cutmats + (int64_t)(payload - 1u) * NE + (int)(d.x >> DESC_KBITS) * ND; \
       if (cut) { prefetch_l1(cm); prefetch_l1(cm + ND - 1); }         /* lands during the closed-form rows of the other lanes */ \
-      if (!coded) row_step<DIM, ORDER>(A, accrow, d, GA, GB);                              \
-      if (cut) cut_row_add<ND>(cm, accrow, d);                                             \
+      if (!coded) row_step<DIM, ORDER, LOWER>(A, accrow, d, GA, GB);                       \
+      if (cut) cut_row_add<ND, LOWER>(cm, accrow, d);                                      \
     }                                                                                      \
   }
 
@@ -451,7 +461,7 @@ __device__ __forceinline__ void header_wait() {
     base3 += __popc(__ballot_sync(0xffffffffu, 2 < myload));                               \
   }
 
-template <int DIM, int ORDER>
+template <int DIM, int ORDER, bool LOWER>
 __global__ void __launch_bounds__(RW * 32, NGSX_MINBLOCKS) k_rows(RowArgs A) {
   constexpr int ND = H1<DIM, ORDER>::ND, NE = ND * ND;
   extern __shared__ __align__(16) double smem_rows[];
@@ -510,10 +520,10 @@ __global__ void __launch_bounds__(RW * 32, NGSX_MINBLOCKS) k_rows(RowArgs A) {
 #undef NGSX_ROW_STEP
 #undef NGSX_ROW_PRIME
 
-template <int DIM, int ORDER>
+template <int DIM, int ORDER, bool LOWER = false>
 static int launch_rows_t(const RowArgs &A, int sm_count, cudaStream_t st) {
   size_t smem = (size_t)RW * (ACCW * sizeof(double) + sizeof(TileHdr));
-  auto kern = k_rows<DIM, ORDER>;
+  auto kern = k_rows<DIM, ORDER, LOWER>;
   NGSX_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   int occ = 0;
   NGSX_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, kern, RW * 32, smem));
@@ -556,6 +566,13 @@ int launch_rows(const ngsx_rowplan *P, int dim, const RuleMom &M, int accumulate
   A.q3d = A.q3aab - A.q3abc;
   A.q4b = 0.5 * (A.q4[2] - 2.0 * A.q4[1] + A.q4[0]);
   A.q4a = A.q4[1] - A.q4[0] - A.q4b;
+  if (P->lower)
+    switch (dim * 100 + P->nd) {
+      case 203: return launch_rows_t<2, 1, true>(A, sm_count, st);
+      case 206: return launch_rows_t<2, 2, true>(A, sm_count, st);
+      case 304: return launch_rows_t<3, 1, true>(A, sm_count, st);
+      case 310: return launch_rows_t<3, 2, true>(A, sm_count, st);
+    }
   switch (dim * 100 + P->nd) {
     case 203: return launch_rows_t<2, 1>(A, sm_count, st);
     case 206: return launch_rows_t<2, 2>(A, sm_count, st);
@@ -622,21 +639,28 @@ int ngsx_rowplan_rowslots(ngsx_rowplan *P, const int32_t **d_rowslot, int64_t *h
 }
 
 static int rowplan_create(int64_t nlist, int32_t nd, const int32_t *table, int64_t ndof, const int64_t *rowptr, const int32_t *colidx,
-                          int64_t row_lo, int64_t row_hi, const int32_t *row_owner, int32_t me, ngsx_rowplan **out, void *stream);
+                          int64_t row_lo, int64_t row_hi, const int32_t *row_owner, int32_t me, ngsx_rowplan **out, void *stream, int lower);
 
 int ngsx_rowplan_create(int64_t nlist, int32_t nd, const int32_t *table, int64_t ndof, const int64_t *rowptr, const int32_t *colidx,
                         int64_t row_lo, int64_t row_hi, ngsx_rowplan **out, void *stream) {
-  return rowplan_create(nlist, nd, table, ndof, rowptr, colidx, row_lo, row_hi, nullptr, 0, out, stream);
+  return rowplan_create(nlist, nd, table, ndof, rowptr, colidx, row_lo, row_hi, nullptr, 0, out, stream, 0);
+}
+
+// the same plan over a LOWER-TRIANGLE pattern (symmetric storage, AddElementMatrixSymmetric, NGS/linalg/sparsematrix_impl.hpp:605-690):
+// rowptr / colidx hold the columns <= row only; the local columns of a pair that lie above its row are skipped by the gather
+int ngsx_rowplan_create_lower(int64_t nlist, int32_t nd, const int32_t *table, int64_t ndof, const int64_t *rowptr, const int32_t *colidx,
+                              int64_t row_lo, int64_t row_hi, ngsx_rowplan **out, void *stream) {
+  return rowplan_create(nlist, nd, table, ndof, rowptr, colidx, row_lo, row_hi, nullptr, 0, out, stream, 1);
 }
 
 int ngsx_rowplan_create_owned(int64_t nlist, int32_t nd, const int32_t *table, int64_t ndof, const int64_t *rowptr, const int32_t *colidx,
                               const int32_t *row_owner, int32_t me, ngsx_rowplan **out, void *stream) {
   if (!row_owner) { set_error("rowplan_create_owned: row_owner is NULL"); return NGSX_ERR_ARG; }
-  return rowplan_create(nlist, nd, table, ndof, rowptr, colidx, 0, -1, row_owner, me, out, stream);
+  return rowplan_create(nlist, nd, table, ndof, rowptr, colidx, 0, -1, row_owner, me, out, stream, 0);
 }
 
 static int rowplan_create(int64_t nlist, int32_t nd, const int32_t *table, int64_t ndof, const int64_t *rowptr, const int32_t *colidx,
-                          int64_t row_lo, int64_t row_hi, const int32_t *row_owner, int32_t me, ngsx_rowplan **out, void *stream) {
+                          int64_t row_lo, int64_t row_hi, const int32_t *row_owner, int32_t me, ngsx_rowplan **out, void *stream, int lower) {
   NGSX_REQUIRE(out && nlist >= 0 && nd > 0 && nd <= 26 && ndof >= 0 && ndof < (1LL << 31) && rowptr, "rowplan_create: bad arguments");
   NGSX_REQUIRE(nlist == 0 || (table && colidx), "rowplan_create: table / colidx are NULL");
   NGSX_REQUIRE(nlist * nd < (1LL << 31), "rowplan_create: more than 2^31 (element, dof) pairs");
@@ -645,7 +669,7 @@ static int rowplan_create(int64_t nlist, int32_t nd, const int32_t *table, int64
   if (row_hi < 0 || row_hi > ndof) row_hi = ndof;
   if (row_lo < 0) row_lo = 0;
   ngsx_rowplan *P = new ngsx_rowplan();
-  P->nlist = nlist; P->nd = nd; P->ndof = ndof; P->ds = nd <= 10 ? 16 : 32; P->rowptr = rowptr;
+  P->nlist = nlist; P->nd = nd; P->ndof = ndof; P->ds = nd <= 10 ? 16 : 32; P->rowptr = rowptr; P->lower = lower;
   *out = P;
   const int64_t nall = nlist * nd;
   if (nall == 0 || row_hi <= row_lo) return NGSX_OK;
@@ -807,7 +831,7 @@ static int rowplan_create(int64_t nlist, int32_t nd, const int32_t *table, int64
   PLAN_CUDA(cudaMemcpyAsync(d_sched, h_sched.data(), nrows * sizeof(RowSched), cudaMemcpyHostToDevice, st));
   PLAN_CUDA(cudaMemsetAsync(P->desc, 0, (size_t)npairs * P->ds, st));
   k_plan_desc<<<(unsigned)((npairs + 127) / 128), 128, 0, st>>>(npairs, nrows, nd, nlist, P->ds, sorted, d_pairptr, d_sched, d_tile_d0, d_tile_so,
-                                                               d_stepoffs, table, rowptr, colidx, P->desc, d_bad);
+                                                               d_stepoffs, table, rowptr, colidx, P->desc, d_bad, P->lower);
   // tile processing order
   PLAN_CUDA(cudaMalloc(&d_ck, P->ntiles * sizeof(uint32_t)));
   PLAN_CUDA(cudaMalloc(&d_ck2, P->ntiles * sizeof(uint32_t)));

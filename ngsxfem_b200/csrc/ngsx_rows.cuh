@@ -34,6 +34,7 @@ struct RuleMom { double m0, m1, m2s, m2d, m3aab, m3abc, m4aabb, m4aabc, m4abcd; 
 struct ngsx_rowplan {
   int64_t nlist = 0, ndof = 0, npairs = 0, nrows = 0, nnz_covered = 0, max_row = 0, nnz_lo = 0, nnz_hi = 0;
   int32_t nd = 0, ds = 0;
+  int32_t lower = 0;                // plan over a lower-triangle (symmetric storage) pattern: columns above the row carry POS_SKIP
   int64_t ntiles = 0;               // non-empty tiles
   int64_t nslots = 0;               // == npairs (no padding)
   int64_t max_steps = 0;
@@ -77,6 +78,7 @@ namespace ngsx {
 #endif
 constexpr int RW = NGSX_RW;                        // warps per CTA of the row kernels
 constexpr int MAXROW = 256;                        // longest supported CSR row (column positions are bytes)
+constexpr int POS_SKIP = 255;                      // lower-triangle plans: this local column has no entry in the row (col > row); rows < 255 entries
 constexpr int ACCW = NGSX_ACCW;                    // doubles of shared memory per warp: the CSR span of one tile
 constexpr int TILE_MAXROWS = NGSX_TILE_MAXROWS;
 constexpr int TILE_MAXPAIRS = NGSX_TILE_MAXPAIRS;

@@ -247,6 +247,7 @@ template <bool PACKED>
 static int dispatch_rows_mats(ngsx_rowplan *plan, const double *mats, int accumulate, double *vals, void *stream) {
   if (plan->nrows == 0 || plan->nlist == 0) return NGSX_OK;
   NGSX_REQUIRE(mats && vals, "assemble_csr_rows_mats: mats / vals are NULL");
+  if (plan->lower) { set_error("assemble_csr_rows_mats: lower-triangle plans are served by ngsx_assemble_csr_rows_h1 only"); return NGSX_ERR_UNSUPPORTED; }
   const DeviceData *dd = device_data();
   if (!dd) return NGSX_ERR_CUDA;
   RowMatArgs A{plan->ntiles, plan->tiles, plan->desc, mats, vals, accumulate};

@@ -589,6 +589,10 @@ class BilinearForm:
 
     def __init__(self, space: H1, symmetric: bool = False, check_unused: bool = False, **_):
         self.space = space
+        # symmetric=True: SparseMatrixSymmetric storage -- the CSR keeps the lower triangle (columns <= row) only and the gather skips
+        # the entries above it (AddElementMatrixSymmetric, NGS/linalg/sparsematrix_impl.hpp:605-690); values are bitwise the lower
+        # triangle of the unsymmetric assembly.  Served by the fused H1 row path (orders 1-2, affine mesh, single GPU).
+        self.symmetric = bool(symmetric)
         self.integrators: List = []
         self.mat: Optional[CSRMatrix] = None
         self._plans: Dict[int, _Plan] = {}
@@ -628,6 +632,8 @@ class BilinearForm:
         g = ctypes.c_void_p()
         check(L.ngsx_csr_graph_create(fes.ndof, ctypes.byref(g)))
         try:
+            if self.symmetric:
+                check(L.ngsx_csr_graph_set_lower(g, 1))
             els = self._graph_elements()
             h1 = self._h1
             tab = h1.el2dof if els is None else h1.el2dof[els].contiguous()
@@ -709,7 +715,12 @@ class BilinearForm:
         table = fes.el2dof[els.long()].contiguous()
         h = ctypes.c_void_p()
         lo, hi = self.row_range if self.row_range is not None else (0, self.space.ndof)
-        if self.row_owner is not None:
+        if self.symmetric:
+            if self.row_owner is not None:
+                raise NgsxError(-2, "symmetric storage with an owner partition is outside the CUDA path")
+            check(L.ngsx_rowplan_create_lower(els.numel(), fes.nd, _ptr(table), self.space.ndof, _ptr(self.mat.rowptr), _ptr(self.mat.colidx),
+                                              lo, hi, ctypes.byref(h), _stream()))
+        elif self.row_owner is not None:
             check(L.ngsx_rowplan_create_owned(els.numel(), fes.nd, _ptr(table), self.space.ndof, _ptr(self.mat.rowptr), _ptr(self.mat.colidx),
                                               _ptr(self.row_owner[0]), int(self.row_owner[1]), ctypes.byref(h), _stream()))
         else:
@@ -729,8 +740,11 @@ class BilinearForm:
             try:
                 plan = self._row_plan(integ)
             except NgsxError as exc:
-                if exc.status != -2:
+                if exc.status != -2 or self.symmetric:
                     raise
+                import warnings
+                warnings.warn("ngsxfem_b200: the owner-computes row plan does not cover this pattern (" + str(exc) +
+                              "); falling back to the coloured scatter, which is several times slower", RuntimeWarning)
                 self.assembly = "colored"              # a CSR row longer than 256 entries: coloured scatter instead
                 return self._plan_for(k, integ)
         elif isinstance(integ, SymbolicCutBFI):
@@ -762,6 +776,8 @@ class BilinearForm:
         fac = torch.nonzero(inner).reshape(-1)
         pe = f2e[fac].contiguous()                                     # [np][2] int32, element 0 = lower number
         npatch = pe.shape[0]
+        if fes.order not in (1, 2):
+            raise NgsxError(-2, "SymbolicFacetPatchBFI: H1 order 1..2 is on the CUDA path (order 3 patches: not built); no CPU fallback")
         nfd = {(2, 1): 2, (2, 2): 3, (3, 1): 3, (3, 2): 6}[(mesh.dim, fes.order)]          # dofs on the shared facet
         ndp = 2 * fes.nd - nfd
         table = torch.empty((npatch, ndp), dtype=torch.int32, device=mesh.device)
@@ -811,6 +827,16 @@ class BilinearForm:
         x_blocks = 0                                               # compound integrators whose IF blocks sit in the shared buffer
         for k, integ in enumerate(self.integrators):
             plan = plans[k]
+            if self.symmetric and not (isinstance(plan, _RowPlan) and isinstance(integ, SymbolicCutBFI) and integ.xterms is None and
+                                       self._deformation_of(integ) is None and fes.order < 3 and self._h1 is fes):
+                raise NgsxError(-2, "symmetric=True is served by the fused H1 row path (SymbolicCutBFI, orders 1-2, affine mesh); no CPU fallback")
+            plain_rows = isinstance(plan, _RowPlan) and not isinstance(integ, SymbolicFacetPatchBFI) and integ.xterms is None and \
+                self._deformation_of(integ) is None and fes.order < 3
+            if gather_after is not None and not plain_rows:
+                # only the fused H1 row path can hold back its gather alone (ngsx_set_gather_wait_event); every other producer
+                # honours the event by waiting for it on the stream before it starts
+                torch.cuda.current_stream().wait_event(gather_after)
+                gather_after = None
             if isinstance(integ, SymbolicFacetPatchBFI):
                 self._assemble_facetpatch(integ, plan)
             elif integ.xterms is not None:

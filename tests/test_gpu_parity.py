@@ -1510,6 +1510,78 @@ def test_order3_tensor_core_kernel_against_fma_kernel(X, dim, nx):
 
 
 @pytest.mark.parametrize("dim,fo", [(2, 1), (2, 2), (3, 1), (3, 2)])
+def test_elvec_thread_kernel_against_warp_kernel(X, dim, fo):
+    """dense element vectors: the thread-per-entry two-pass kernels (k_elvec_t) against the warp-per-element kernel (k_elvec, checked
+    against the oracle by the linear-form tests), all domains, point counts included"""
+    m = X.meshes.MakeStructured2DMesh(11) if dim == 2 else X.meshes.MakeStructured3DMesh(5)
+    mesh = X.ngs.Mesh(m)
+    gf = X.ngs.GridFunction(X.ngs.H1(mesh, order=1))
+    X.xfem.InterpolateToP1(X.ngs.SphereLevelset((0.5,) * dim, 0.34), gf)
+    L = X.lib.load()
+    st = torch.cuda.current_stream().cuda_stream
+    nd = X.ngs.H1(mesh, order=fo).nd
+    els = torch.arange(mesh.ne - 1, -1, -1, dtype=torch.int32, device="cuda")            # a permuted list
+    poly = X.lib.make_poly([(1.0, 0, 0, 0), (0.7, 1, 1, 0), (-0.3, 0, 2, 1 if dim == 3 else 0)])
+    try:
+        for dt in (NEG, POS, IF):
+            res = []
+            for warp in (1, 0):
+                L.ngsx_debug_set_elvec_warp(warp)
+                ev = torch.full((mesh.ne, nd), float("nan"), dtype=torch.float64, device="cuda")
+                npts = torch.full((mesh.ne,), -7, dtype=torch.int32, device="cuda")
+                X.lib.check(L.ngsx_elvec_h1(ctypes.byref(mesh.c_struct()), gf.vec.data_ptr(), fo, dt, 2 * fo, ctypes.byref(poly), mesh.ne,
+                                            els.data_ptr(), ev.data_ptr(), npts.data_ptr(), st))
+                res.append((ev.cpu().numpy(), npts.cpu().numpy()))
+            (ref, rn), (got, gn) = res
+            assert np.array_equal(rn, gn) and np.abs(ref).max() > 0
+            assert relerr_rows(got, ref) <= RTOL
+    finally:
+        L.ngsx_debug_set_elvec_warp(0)
+
+
+@pytest.mark.parametrize("dim,fo", [(2, 1), (2, 2), (3, 1), (3, 2)])
+def test_symmetric_storage_is_the_lower_triangle(X, dim, fo):
+    """BilinearForm(symmetric=True): SparseMatrixSymmetric storage (AddElementMatrixSymmetric, NGS/linalg/sparsematrix_impl.hpp:605-690) --
+    pattern = the columns <= row of the unsymmetric pattern, values BITWISE the lower triangle of the unsymmetric assembly (same plan
+    order per entry), also after the level set moved, also restricted; unsupported combinations raise"""
+    m = X.meshes.MakeStructured2DMesh(13) if dim == 2 else X.meshes.MakeStructured3DMesh(6)
+    mesh = X.ngs.Mesh(m)
+    gf = X.ngs.GridFunction(X.ngs.H1(mesh, order=1))
+    X.xfem.InterpolateToP1(X.ngs.SphereLevelset((0.5,) * dim, 0.33), gf)
+    Vh = X.ngs.H1(mesh, order=fo)
+    u, v = Vh.TnT()
+    h = X.ngs.specialcf.mesh_size
+    for dt, form in ((NEG, 0.7 * X.ngs.grad(u) * X.ngs.grad(v) + 1.3 * u * v), (IF, (1.0 / h) * u * v + 0.2 * X.ngs.grad(u) * X.ngs.grad(v))):
+        ci = X.xfem.CutInfo(mesh, gf)
+        restr = ci.GetElementsOfType(X.xfem.HASNEG if dt == NEG else X.xfem.IF)
+        forms = []
+        for sym in (False, True):
+            a = X.xfem.RestrictedBilinearForm(Vh, element_restriction=restr, symmetric=sym)
+            a += X.xfem.SymbolicBFI(levelset_domain={"levelset": gf, "domain_type": dt}, form=form)
+            a.Assemble()
+            assert a.assembly == "rows"
+            forms.append(a)
+        full, low = forms
+        rp, ci_, va = (t.cpu().numpy() for t in (full.mat.rowptr, full.mat.colidx, full.mat.vals))
+        rows = np.repeat(np.arange(Vh.ndof), np.diff(rp))
+        keep = ci_ <= rows
+        assert low.mat.nnz == int(keep.sum()) and low.mat.nnz < full.mat.nnz
+        assert np.array_equal(low.mat.colidx.cpu().numpy(), ci_[keep])
+        assert np.array_equal(low.mat.rowptr.cpu().numpy(), np.concatenate([[0], np.cumsum(np.bincount(rows[keep], minlength=Vh.ndof))]))
+        assert np.array_equal(low.mat.vals.cpu().numpy(), va[keep])                          # bitwise
+        gf.vec += 0.01                                                                        # the level set moves: same plans
+        full.Assemble(); low.Assemble()
+        assert np.array_equal(low.mat.vals.cpu().numpy(), full.mat.vals.cpu().numpy()[keep])
+        gf.vec -= 0.01
+    with pytest.raises(X.lib.NgsxError):
+        Vd = X.ngs.H1(mesh, order=1, dgjumps=True)
+        ud, vd = Vd.TnT()
+        b = X.xfem.BilinearForm(Vd, symmetric=True)
+        b += X.xfem.SymbolicFacetPatchBFI(form=0.1 * (ud - ud.Other()) * (vd - vd.Other()), skeleton=False)
+        b.Assemble()
+
+
+@pytest.mark.parametrize("dim,fo", [(2, 1), (2, 2), (3, 1), (3, 2)])
 def test_packed_rows_equal_dense_blocks(X, dim, fo):
     """the two sources of the matrix gather (dense blocks fetched per lane / packed rows written by the producer at the slots of
     the schedule) give bitwise the same CSR values: same plan, same summation order"""
