@@ -217,6 +217,28 @@ def run_b200(args):
     sweep_mode = os.environ.get("NGSX_BENCH_SWEEPS", "fused")
     fused_list = [(xfem.IF, 4, 1.0), (xfem.NEG, 4, 1.0)]
 
+    # N > 1: the scalar totals of Integrate() cross the GPUs through peer-memory mailboxes written by the last kernel of the rank's
+    # step (ngsxfem_b200/peer.py, csrc/ngsx_peer.cu) -- no NCCL call, no host work per step.  Measured at N = 8 (same box, graph
+    # replay): NCCL all-reduce per step 0.214 ms, no exchange at all 0.173 ms.  NGSX_BENCH_EXCHANGE=nccl switches back (A/B).
+    peer, exchange_note = None, "none (single GPU)"
+    if world > 1:
+        exchange_note = "NCCL all-reduce of the two Integrate() scalars per step, on its own stream"
+        if os.environ.get("NGSX_BENCH_NOALLREDUCE"):
+            exchange_note = "none (NGSX_BENCH_NOALLREDUCE: A/B switch)"
+        elif os.environ.get("NGSX_BENCH_EXCHANGE", "peer") == "peer" and sweep_mode == "fused":
+            try:
+                from ngsxfem_b200.peer import PeerExchange
+                peer = PeerExchange(rank, world, dev)
+                exchange_note = ("peer-memory mailboxes (CUDA IPC over NVLink): the step's last kernel publishes the rank's two sums to every peer and "
+                                 "collects the previous step's totals in rank order; no collective call per step")
+            except Exception as exc:                                     # IPC not permitted in this container: stay on NCCL
+                peer = None
+                exchange_note += f" (peer-memory exchange unavailable: {type(exc).__name__}: {str(exc)[:120]})"
+        ok = torch.tensor([1 if peer is not None else 0], device=dev)
+        dist.all_reduce(ok, op=dist.ReduceOp.MIN)                        # all ranks or none
+        if int(ok.item()) == 0 and peer is not None:
+            peer.close(); peer = None
+
     def step(record, serial=serial, timing=True, order=order_default):
         mk = ev if timing else (lambda: torch.cuda.Event())              # no timing events inside a graph capture
         e = [mk() for _ in range(6)]
@@ -224,7 +246,10 @@ def run_b200(args):
         e[0].record()
         if sweep_mode == "fused":
             if serial:
-                r = xfem.UpdateAndIntegrate(ci, lsetp1, fused_list); e[1].record()
+                r = xfem.UpdateAndIntegrate(ci, lsetp1, fused_list)
+                if peer is not None:
+                    peer.exchange(r)
+                e[1].record()
                 a.Assemble(); e[2].record(); e[3].record(); e[4].record()
             else:
                 if order == "after":
@@ -233,7 +258,10 @@ def run_b200(args):
                 else:
                     side[0].wait_event(e[0])
                 with torch.cuda.stream(side[0]):
-                    r = xfem.UpdateAndIntegrate(ci, lsetp1, fused_list); e[1].record(); e[3].record(); e[4].record()
+                    r = xfem.UpdateAndIntegrate(ci, lsetp1, fused_list)
+                    if peer is not None:
+                        peer.exchange(r)
+                    e[1].record(); e[3].record(); e[4].record()
                 if order == "join":
                     a.Assemble(gather_after=e[4]); e[2].record()
                 elif order != "after":
@@ -305,7 +333,7 @@ def run_b200(args):
                 raise RuntimeError(f"graph replay differs from the eager step {chk} {int(wrote.sum())} {plan.nnz_covered}")
             a.mat.vals.copy_(ref_vals)
             del wrote
-            graph_note = f"CUDA graph per rank (assembly chain + three forked sweep streams, order '{order_default}', sweeps {sweep_mode}), NCCL all-reduce outside"
+            graph_note = f"CUDA graph per rank (assembly chain + three forked sweep streams, order '{order_default}', sweeps {sweep_mode}), " + ("scalar exchange inside (peer mailboxes)" if peer is not None else "NCCL all-reduce outside")
             del ref_vals
         except Exception as exc:                                         # capture unsupported on this driver: stay eager
             graph, graph_note = None, f"eager (graph capture failed: {type(exc).__name__}: {str(exc)[:200]})"
@@ -316,11 +344,23 @@ def run_b200(args):
             dist.barrier()
         torch.cuda.synchronize()
 
+    w_out = None
     for _ in range(args.warmup):
         if graph is not None:
             graph.replay()
         else:
-            step(None)
+            w_out = step(None)
+    if peer is not None:                                 # the mailbox totals against an NCCL all-reduce of the same local sums, once, untimed
+        loc = torch.cat(g_out if graph is not None else w_out).clone()
+        tot = peer.collect_last(2).clone()
+        dist.all_reduce(loc)
+        allt = [torch.zeros_like(tot) for _ in range(world)]
+        dist.all_gather(allt, tot)
+        same = all(torch.equal(allt[0], x) for x in allt)
+        close = bool(((tot - loc).abs() <= 1e-12 * loc.abs()).all())
+        if not (same and close):
+            raise RuntimeError(f"peer-memory exchange differs from the NCCL all-reduce: {tot.tolist()} vs {loc.tolist()} (bitwise equal across ranks: {same})")
+        exchange_note += "; totals checked against an NCCL all-reduce (<= 1e-12 relative, bitwise equal on all ranks)"
     barrier()
     sampler = ClockSampler(lrank)
     sampler.start()
@@ -337,7 +377,7 @@ def run_b200(args):
             s_if, s_neg = g_out
         else:
             s_if, s_neg = step(rec)
-        if world > 1:                                    # the path's only exchange at this tier: scalar Integrate() all-reduce
+        if world > 1 and peer is None and not os.environ.get("NGSX_BENCH_NOALLREDUCE"):   # NCCL variant of the exchange (A/B; peer mailboxes are inside the step)
             sc = torch.cat([s_if, s_neg])                # (copies the two scalars out of the graph's static buffers)
             if comm is None:
                 dist.all_reduce(sc)
@@ -348,6 +388,8 @@ def run_b200(args):
                 sc.record_stream(comm)
     if comm is not None:
         main.wait_stream(comm)
+    if peer is not None:
+        g_tot = peer.collect_last(2)                     # totals of the last step (every earlier step's were collected by its successor)
     t_end.record()
     barrier()
     if world == 1:
@@ -554,14 +596,14 @@ def run_b200(args):
         "config": {"workload": workload_name(args.nx, mesh.ne, n_global),
                    "ne": mesh.ne, "hasneg_elements": n_global, "nnz": nnz_global, "assembly": a.assembly, "group": args.group, "colors": plan.ncolors,
                    "setup_s_untimed": round(setup_s, 2), "stage_ms": {"classify": cl_ms, "assemble": as_ms, "integrate": in_ms},
-                   "stage_ms_one_stream": serial_break, "launch": graph_note, "per_rank": per_rank, "numa": numa_note,
+                   "stage_ms_one_stream": serial_break, "launch": graph_note, "exchange": exchange_note, "per_rank": per_rank, "numa": numa_note,
                    "sweeps": {"fused": "CutInfo.Update + Integrate(IF) + Integrate(NEG) in one pass over the element table (xfem.UpdateAndIntegrate / ngsx_classify_integrate, bitwise the separate calls); stage_ms.classify is that pass, stage_ms.integrate is 0",
                               "separate": "three calls"}[sweep_mode],
                    "streams": "1 (serial stages)" if serial else {"join": "CutInfo.Update | Integrate(IF) | Integrate(NEG) on three streams beside k_geom + k_cutmat; the row gather waits for them (ngsx_set_gather_wait_event) and runs alone; stage_ms = step start to the stage's last kernel, 'assemble' therefore contains the wait",
                                                                      "after": "assemble, then CutInfo.Update | Integrate(IF) | Integrate(NEG) on three streams; stage_ms = stage start to its last kernel (the three sweeps overlap)",
                                                                      "with": "the three sweeps on three streams beside the whole assembly chain"}[order_default],
                    "l2": "inputs larger than L2 (CSR values + pair descriptors + mesh > 1.4 GB touched per step vs 126 MB L2); no explicit flush",
-                   "partition": "owner-computes: contiguous chunks of equal cost (cut element = 3.2 uncut) of the HASNEG element list per rank, a CSR row belongs to the rank of the first listed element touching it, halo elements re-evaluated, no interface-row exchange; element blocks for Integrate, scalars all-reduced (NCCL)"},
+                   "partition": "owner-computes: contiguous chunks of equal cost (cut element = 3.2 uncut) of the HASNEG element list per rank, a CSR row belongs to the rank of the first listed element touching it, halo elements re-evaluated, no interface-row exchange; element blocks for Integrate, the two scalars exchanged between the ranks every step (config.exchange)"},
         "roofline": {"bound": "hbm", "kernel": "k_rows<3,2> (owner-computes row gather: every CSR value of the assembled operator written once)",
                      "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": traffic,
                      "peak_source": peak_src, "algorithmic_bytes_per_element": ALGO_BYTES_SCATTER,

@@ -330,6 +330,23 @@ int ngsx_st_elmat_h1(const ngsx_mesh *mesh, const double *lset_st, int ntime_dof
  * space-time rules of order 0 in space and time_order in time -> dom [ne] int8 (NEG / POS / IF), cut ratio [ne] */
 int ngsx_st_classify(const ngsx_mesh *mesh, const double *lset_st, int ntime_dofs, int time_order, int8_t *dom, double *ratio, void *stream);
 
+/* ---- (e) the exchange between the GPUs of one node -------------------------------------------------------------------
+ * The reference's Integrate() sums over MPI ranks with a collective (cutint/python_cutint.cpp:66-70: AllReduce of the local sums).
+ * Here each rank owns a mailbox in device memory, exported / mapped with CUDA IPC; ngsx_peer_exchange -- the last node of a rank's
+ * captured step -- publishes the rank's n <= NGSX_PEER_MAXVALS local sums into every peer's mailbox with plain stores over NVLink
+ * and collects the totals of the PREVIOUS step (out_prev, rank order: bitwise equal on all ranks); ngsx_peer_collect delivers the
+ * totals of the last published step.  d_step: device counter, 0 before the first exchange, incremented by the kernel (replays of a
+ * CUDA graph therefore advance it).  All ranks must call it once per step.  A peer that never publishes yields NaN, not a hang. */
+#define NGSX_PEER_MAXVALS 4
+int ngsx_peer_mailbox_bytes(int world);
+int ngsx_peer_alloc(int world, void **mailbox, unsigned char *handle64 /* cudaIpcMemHandle_t, to be sent to the peers */);
+int ngsx_peer_open(const unsigned char *handle64, void **mailbox);
+int ngsx_peer_close(void *mailbox);
+int ngsx_peer_free(void *mailbox);
+int ngsx_peer_exchange(const double *local, int n, int rank, int world, void *const *d_peers, void *mailbox, int64_t *d_step, double *out_prev,
+                       void *stream);
+int ngsx_peer_collect(void *mailbox, int n, int world, const int64_t *d_step, double *out, void *stream);
+
 /* ---- (f-5) quadrilaterals / hexahedra ------------------------------------------------------------------------------
  * LevelsetCutQuadrilateral (cutint/straightcutrule.cpp:206-501, policy FIND_OPTIMAL) and the ET_QUAD / ET_HEX branch of
  * StraightCutIntegrationRule[Untransformed] (:580-726).  For these entry points mesh->el2v is [ne][4] (dim 2) / [ne][8] (dim 3)

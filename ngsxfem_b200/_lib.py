@@ -116,6 +116,13 @@ SIGNATURES = {
                                    c_void_p, c_int, c_void_p, c_void_p]),
     "ngsx_st_rule_count": (c_int, [ctypes.POINTER(Mesh), c_void_p, c_int, c_int, c_int, c_int, c_void_p, c_void_p]),
     "ngsx_st_rule_fill": (c_int, [ctypes.POINTER(Mesh), c_void_p, c_int, c_int, c_int, c_int, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p]),
+    "ngsx_peer_mailbox_bytes": (c_int, [c_int]),
+    "ngsx_peer_alloc": (c_int, [c_int, ctypes.POINTER(c_void_p), c_void_p]),
+    "ngsx_peer_open": (c_int, [c_void_p, ctypes.POINTER(c_void_p)]),
+    "ngsx_peer_close": (c_int, [c_void_p]),
+    "ngsx_peer_free": (c_int, [c_void_p]),
+    "ngsx_peer_exchange": (c_int, [c_void_p, c_int, c_int, c_int, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p]),
+    "ngsx_peer_collect": (c_int, [c_void_p, c_int, c_int, c_void_p, c_void_p, c_void_p]),
     "ngsx_st_elmat_h1": (c_int, [ctypes.POINTER(Mesh), c_void_p, c_int, c_int, c_int, c_int, c_int, c_int, c_double, c_double, c_double, c_i64,
                                  c_void_p, c_void_p, c_void_p]),
     "ngsx_st_classify": (c_int, [ctypes.POINTER(Mesh), c_void_p, c_int, c_int, c_void_p, c_void_p, c_void_p]),

@@ -1509,6 +1509,41 @@ def test_order3_tensor_core_kernel_against_fma_kernel(X, dim, nx):
         L.ngsx_debug_set_fast_path(1)
 
 
+def test_peer_exchange_single_rank(X):
+    """the mailbox exchange of the Integrate() scalars (csrc/ngsx_peer.cu) with world = 1: the kernel publishes into its own mailbox,
+    delivers the PREVIOUS step's totals, survives more steps than it has slots, and replays inside a CUDA graph (the step counter
+    lives on the device).  The multi-rank path (CUDA IPC mappings of the peers' mailboxes) is checked against an NCCL all-reduce
+    inside bench.py at every N > 1."""
+    from ngsxfem_b200.peer import PeerExchange
+    px = PeerExchange(0, 1, "cuda:0")
+    try:
+        vals = [torch.tensor([1.5 + k, -2.25 * k], dtype=torch.float64, device="cuda") for k in range(7)]
+        for k, v in enumerate(vals):
+            prev = px.exchange(v)
+            torch.cuda.synchronize()
+            if k > 0:
+                assert torch.equal(prev[:2], vals[k - 1])
+            assert torch.equal(px.collect_last(2), v) and int(px.step.item()) == k + 1
+        buf = torch.zeros(2, dtype=torch.float64, device="cuda")
+        g = torch.cuda.CUDAGraph()
+        s = torch.cuda.Stream()
+        with torch.cuda.stream(s):
+            with torch.cuda.graph(g, stream=s):
+                px.exchange(buf)
+        for k in range(5):
+            buf.copy_(torch.tensor([10.0 + k, 0.5 * k], dtype=torch.float64))
+            g.replay()
+            torch.cuda.synchronize()
+            assert int(px.step.item()) == 8 + k
+            assert torch.equal(px.collect_last(2).cpu(), torch.tensor([10.0 + k, 0.5 * k], dtype=torch.float64))
+            if k > 0:
+                assert torch.equal(px.prev[:2].cpu(), torch.tensor([10.0 + k - 1, 0.5 * (k - 1)], dtype=torch.float64))
+        with pytest.raises(X.lib.NgsxError):
+            px.exchange(torch.zeros(5, dtype=torch.float64, device="cuda"))
+    finally:
+        px.close()
+
+
 @pytest.mark.parametrize("dim,fo", [(2, 1), (2, 2), (3, 1), (3, 2)])
 def test_elvec_thread_kernel_against_warp_kernel(X, dim, fo):
     """dense element vectors: the thread-per-entry two-pass kernels (k_elvec_t) against the warp-per-element kernel (k_elvec, checked
