@@ -908,7 +908,7 @@ def test_unsupported_paths_raise(X):
     with pytest.raises(X.lib.NgsxError):
         X.xfem.Integrate(levelset_domain={"levelset": gf, "domain_type": IF, "subdivlvl": 2}, cf=1.0, mesh=mesh, order=2)
     with pytest.raises(X.lib.NgsxError):
-        X.xfem.CutInfo(mesh, gf, time_order=2)
+        X.xfem.CutInfo(mesh, X.ngs.GridFunction(X.ngs.H1(mesh, order=2)), time_order=2)                     # space-time level sets are P1 in space
     with pytest.raises(X.lib.NgsxError):
         X.xfem.Integrate(levelset_domain={"levelset": gf, "domain_type": IF}, cf=1.0, mesh=mesh, order=40)   # rule not tabulated
     gf.vec.zero_()                                                                                          # all-zero level set: reference throws
