@@ -149,7 +149,8 @@ __global__ void __launch_bounds__(FP_WARPS * 32) k_facetpatch_c(ngsx_mesh M, con
                                                                int64_t npatch, const int32_t *__restrict__ patch_els,
                                                                const uint8_t *__restrict__ cidx, double *__restrict__ mats,
                                                                const int32_t *__restrict__ rowslot) {
-  constexpr int ND = H1<DIM, ORDER>::ND, NFD = DIM == 2 ? (ORDER == 1 ? 2 : 3) : (ORDER == 1 ? 3 : 6);   // dofs on the shared facet
+  // dofs on the shared facet: vertices + (order - 1) per edge (+ one face function of a tet face at order 3)
+  constexpr int ND = H1<DIM, ORDER>::ND, NFD = DIM == 2 ? ORDER + 1 : (ORDER == 1 ? 3 : (ORDER == 2 ? 6 : 10));
   constexpr int NP = 2 * ND - NFD, NE = NP * NP, NS = NP * (NP + 1) / 2, T = (NS + 31) / 32;   // symmetric: upper triangle only
   extern __shared__ __align__(16) unsigned char smem_raw[];
   double4 *srule = reinterpret_cast<double4 *>(smem_raw);
@@ -171,9 +172,15 @@ __global__ void __launch_bounds__(FP_WARPS * 32) k_facetpatch_c(ngsx_mesh M, con
     double p[2][DIM + 1][DIM];
     ElGeom<DIM> G[2];
     double hfac[2];
+    unsigned orient[2] = {0u, 0u};                  // order 3: edge orientations from the global vertex numbers of each element
     for (int s = 0; s < 2; s++) {
       load_el_geo<DIM>(M, patch_els[2 * k + s], p[s]);
       element_geometry<DIM>(p[s], G[s]);
+      if constexpr (ORDER == 3) {
+        int vn[4] = {0, 0, 0, 0};
+        for (int m = 0; m <= DIM; m++) vn[m] = __ldg(M.el2v + (int64_t)patch_els[2 * k + s] * (DIM + 1) + m);
+        orient[s] = edge_orientation<DIM>(vn);
+      }
     }
     {
       const double m0 = fabs(G[0].det);
@@ -216,8 +223,8 @@ __global__ void __launch_bounds__(FP_WARPS * 32) k_facetpatch_c(ngsx_mesh M, con
         double *jc = stage + lane * NP;
         for (int c = 0; c < NP; c++) jc[c] = 0.0;
         for (int i = 0; i < ND; i++) {
-          jc[ci[side * ND + i]] += h1_shape<DIM, ORDER>(i, lam);
-          jc[ci[(1 - side) * ND + i]] -= h1_shape<DIM, ORDER>(i, lo);
+          jc[ci[side * ND + i]] += h1_shape<DIM, ORDER>(i, lam, orient[side]);
+          jc[ci[(1 - side) * ND + i]] -= h1_shape<DIM, ORDER>(i, lo, orient[1 - side]);
         }
         facq[lane] = hfac[side] * r.w;
       }
@@ -251,7 +258,7 @@ __global__ void __launch_bounds__(FP_WARPS * 32) k_facetpatch_c(ngsx_mesh M, con
 template <int DIM, int ORDER>
 static int launch_fpc(const ngsx_mesh &M, const DeviceData *dd, const double4 *rule, int nr, double coef, int hpow, int64_t np,
                       const int32_t *patch_els, const uint8_t *cidx, int ndp, double *mats, const int32_t *rowslot, cudaStream_t st) {
-  constexpr int ND = H1<DIM, ORDER>::ND, NFD = DIM == 2 ? (ORDER == 1 ? 2 : 3) : (ORDER == 1 ? 3 : 6), NP = 2 * ND - NFD;
+  constexpr int ND = H1<DIM, ORDER>::ND, NFD = DIM == 2 ? ORDER + 1 : (ORDER == 1 ? 3 : (ORDER == 2 ? 6 : 10)), NP = 2 * ND - NFD;
   if (ndp != NP) { set_error("facetpatch_cmat: ndp does not match the merged dof count of this element type"); return NGSX_ERR_ARG; }
   size_t smem = (size_t)nr * 32 + (size_t)FP_WARPS * (32 * NP + 32) * 8;
   auto kern = k_facetpatch_c<DIM, ORDER>;
@@ -488,7 +495,7 @@ extern "C" int ngsx_facetpatch_cmat_h1(const ngsx_mesh *mesh, int fe_order, doub
                                        const int32_t *patch_els, const uint8_t *cidx, int32_t ndp, double *mats, void *stream) {
   NGSX_REQUIRE(mesh && (mesh->dim == 2 || mesh->dim == 3) && mesh->vert && mesh->el2v, "facetpatch_cmat: bad mesh");
   NGSX_REQUIRE(npatch >= 0 && (npatch == 0 || (patch_els && cidx && mats)), "facetpatch_cmat: bad arguments");
-  if (fe_order < 1 || fe_order > 2) { set_error("facetpatch_cmat: H1 order outside the CUDA path (1, 2)"); return NGSX_ERR_UNSUPPORTED; }
+  if (fe_order < 1 || fe_order > 3) { set_error("facetpatch_cmat: H1 order outside the CUDA path (1, 2, 3)"); return NGSX_ERR_UNSUPPORTED; }
   const DeviceData *dd = device_data();
   if (!dd) return NGSX_ERR_CUDA;
   const double4 *rule; int nr;
@@ -501,6 +508,8 @@ extern "C" int ngsx_facetpatch_cmat_h1(const ngsx_mesh *mesh, int fe_order, doub
     case 22: return launch_fpc<2, 2>(*mesh, dd, rule, nr, coef, hpow, npatch, patch_els, cidx, ndp, mats, rowslot, st);
     case 31: return launch_fpc<3, 1>(*mesh, dd, rule, nr, coef, hpow, npatch, patch_els, cidx, ndp, mats, rowslot, st);
     case 32: return launch_fpc<3, 2>(*mesh, dd, rule, nr, coef, hpow, npatch, patch_els, cidx, ndp, mats, rowslot, st);
+    case 23: return launch_fpc<2, 3>(*mesh, dd, rule, nr, coef, hpow, npatch, patch_els, cidx, ndp, mats, rowslot, st);
+    case 33: return launch_fpc<3, 3>(*mesh, dd, rule, nr, coef, hpow, npatch, patch_els, cidx, ndp, mats, rowslot, st);   // 30 merged dofs: dense blocks only (the gather's descriptors end at 26)
   }
   return NGSX_ERR_UNSUPPORTED;
 }

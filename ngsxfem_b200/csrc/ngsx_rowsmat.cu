@@ -262,9 +262,11 @@ static int dispatch_rows_mats(ngsx_rowplan *plan, const double *mats, int accumu
     case 10: return launch_rows_mats_t<10, PACKED>(A, dd->sm_count, st);
     case 12: return launch_rows_mats_t<12, PACKED>(A, dd->sm_count, st);
     case 14: return launch_rows_mats_t<14, PACKED>(A, dd->sm_count, st);
+    case 16: return launch_rows_mats_t<16, PACKED>(A, dd->sm_count, st);
+    case 18: return launch_rows_mats_t<18, PACKED>(A, dd->sm_count, st);
     case 20: return launch_rows_mats_t<20, PACKED>(A, dd->sm_count, st);
   }
-  set_error("assemble_csr_rows_mats: unsupported block size (3, 4, 5, 6, 8, 9, 10, 12, 14, 20)");
+  set_error("assemble_csr_rows_mats: unsupported block size (3, 4, 5, 6, 8, 9, 10, 12, 14, 16, 18, 20)");
   return NGSX_ERR_UNSUPPORTED;
 }
 

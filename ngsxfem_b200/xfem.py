@@ -776,9 +776,10 @@ class BilinearForm:
         fac = torch.nonzero(inner).reshape(-1)
         pe = f2e[fac].contiguous()                                     # [np][2] int32, element 0 = lower number
         npatch = pe.shape[0]
-        if fes.order not in (1, 2):
-            raise NgsxError(-2, "SymbolicFacetPatchBFI: H1 order 1..2 is on the CUDA path (order 3 patches: not built); no CPU fallback")
-        nfd = {(2, 1): 2, (2, 2): 3, (3, 1): 3, (3, 2): 6}[(mesh.dim, fes.order)]          # dofs on the shared facet
+        if (mesh.dim, fes.order) not in ((2, 1), (2, 2), (3, 1), (3, 2), (2, 3)):
+            raise NgsxError(-2, "SymbolicFacetPatchBFI: H1 order 1..2 (and order 3 on triangles) is on the CUDA path -- a P3 tet patch has 30 "
+                                "merged dofs, the gather's descriptors end at 26; no CPU fallback")
+        nfd = {(2, 1): 2, (2, 2): 3, (3, 1): 3, (3, 2): 6, (2, 3): 4}[(mesh.dim, fes.order)]          # dofs on the shared facet
         ndp = 2 * fes.nd - nfd
         table = torch.empty((npatch, ndp), dtype=torch.int32, device=mesh.device)
         cidx = torch.empty((npatch, 2 * fes.nd), dtype=torch.uint8, device=mesh.device)

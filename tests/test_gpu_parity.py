@@ -343,10 +343,12 @@ def test_facet_marking_and_patches(X):
         assert diff <= 1e-11 * abs(A).max()
 
 
-@pytest.mark.parametrize("dim,fo", [(2, 1), (2, 2), (3, 1), (3, 2)])
+@pytest.mark.parametrize("dim,fo", [(2, 1), (2, 2), (3, 1), (3, 2), (2, 3)])
 def test_ghost_penalty_row_gather(X, dim, fo):
     """f-1: fictitious-domain operator = NEG stiffness + ghost-penalty facet patches (py_tutorials/fictdom_ghostpen.py:86-107),
-    both through the owner-computes row gather; merged patch blocks vs C em C^T of the oracle's CalcFacetMatrix restatement."""
+    both through the owner-computes row gather; merged patch blocks vs C em C^T of the oracle's CalcFacetMatrix restatement.
+    (2, 3) is the tutorial's own setting (order 3, ring level set on [-1,1]^2) on the undeformed mesh: order-3 patches carry the
+    edge orientations of both elements, the order-3 volume blocks come from k_elmat3_fast / k_elmat3."""
     from oracle import orc
     import scipy.sparse as sp
     if dim == 2:
