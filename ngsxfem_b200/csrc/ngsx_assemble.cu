@@ -1683,6 +1683,13 @@ static cudaEvent_t g_evr[TIMING_RING][4];
 static cudaEvent_t *g_ev = g_evr[0];
 static int g_ev_calls = 0;      // timed calls since the last ngsx_debug_get_timing
 static bool g_ev_ready = false;
+// a timing event on the launch stream; under stream capture an EXTERNAL event-record node, so that the events of a replayed
+// CUDA graph carry the times of the last replay and cudaEventElapsedTime stays legal
+static void record_timing_event(cudaEvent_t e, cudaStream_t st) {
+  cudaStreamCaptureStatus cs = cudaStreamCaptureStatusNone;
+  if (cudaStreamIsCapturing(st, &cs) == cudaSuccess && cs == cudaStreamCaptureStatusActive) cudaEventRecordWithFlags(e, st, cudaEventRecordExternal);
+  else cudaEventRecord(e, st);
+}
 static thread_local cudaEvent_t g_gather_wait = nullptr;      // one-shot: see ngsx_set_gather_wait_event
 
 }  // namespace ngsx
@@ -1791,7 +1798,7 @@ int ngsx_assemble_csr_rows_h1(const ngsx_mesh *mesh, const double *lset_v, int f
   const bool sym_rule = rule_moments(dim, intorder, &mom);
   const int use_fast = g_use_fast && sym_rule && h_form->c_nitsche == 0.0 && h_form->c_dndn == 0.0 && dt != IF;
   // 1. geometry records + quadrature work list, 2. cut-element matrices, 3. row gather
-  if (g_timing) { g_ev = g_evr[g_ev_calls % TIMING_RING]; g_ev_calls++; cudaEventRecord(g_ev[0], st); }
+  if (g_timing) { g_ev = g_evr[g_ev_calls % TIMING_RING]; g_ev_calls++; record_timing_event(g_ev[0], st); }
   auto *e = reinterpret_cast<unsigned long long *>(err);
   const unsigned nb = (unsigned)((nlist + 255) / 256);
   auto geom = [&]() -> int {
@@ -1816,7 +1823,7 @@ int ngsx_assemble_csr_rows_h1(const ngsx_mesh *mesh, const double *lset_v, int f
     if (int rc = rows_reserve_cut(plan, want)) return rc;
   }
   if (int rc = geom()) return rc;
-  if (g_timing) cudaEventRecord(g_ev[1], st);
+  if (g_timing) record_timing_event(g_ev[1], st);
   ElmatArgs A{};
   A.M = *mesh; A.lset = lset_v; A.tab = dd->cut_table; A.dt = dt;
   A.rule_vol = rv; A.nr_vol = nv; A.rule_if = ri; A.nr_if = ni;
@@ -1826,9 +1833,9 @@ int ngsx_assemble_csr_rows_h1(const ngsx_mesh *mesh, const double *lset_v, int f
   // the work-list length lives on the device: launch the persistent grid for the worst case, idle CTAs leave at once
   if (int rc = launch_cutmat(A, fe_order, dd->sm_count, plan->cut_cap, st)) return rc;
   if (gather_wait) NGSX_CUDA(cudaStreamWaitEvent(st, gather_wait, 0));      // the gather starts once the caller's side work is done
-  if (g_timing) cudaEventRecord(g_ev[2], st);
+  if (g_timing) record_timing_event(g_ev[2], st);
   const int rc = launch_rows(plan, dim, mom, accumulate, vals, dd->sm_count, st);
-  if (g_timing) cudaEventRecord(g_ev[3], st);
+  if (g_timing) record_timing_event(g_ev[3], st);
   return rc;
 }
 
