@@ -322,7 +322,8 @@ def run_b200(args):
             ref_vals = a.mat.vals.clone()
             torch.cuda.synchronize()
             graph = torch.cuda.CUDAGraph()
-            L.ngsx_debug_set_timing(1)                                   # (resets the library's call counter: the capture is call 0)
+            if pworld == 1:                                              # N > 1: no event nodes in the short per-rank graphs (kernel times from eager steps after)
+                L.ngsx_debug_set_timing(1)                               # (resets the library's call counter: the capture is call 0)
             lps0 = L.ngsx_launch_count()
             with torch.cuda.graph(graph):
                 g_out = step(None, serial=False, timing=False)
@@ -337,7 +338,7 @@ def run_b200(args):
                 raise RuntimeError(f"graph replay differs from the eager step {chk} {int(wrote.sum())} {plan.nnz_covered}")
             a.mat.vals.copy_(ref_vals)
             del wrote
-            graph_timing = True
+            graph_timing = pworld == 1
             graph_note = f"CUDA graph per rank (assembly chain + three forked sweep streams, order '{order_default}', sweeps {sweep_mode}), " + ("scalar exchange inside (peer mailboxes)" if peer is not None else "NCCL all-reduce outside")
             del ref_vals
         except Exception as exc:                                         # capture unsupported on this driver: stay eager
