@@ -149,6 +149,11 @@ int ngsx_elmat_h1(const ngsx_mesh *mesh, const double *lset_v, int fe_order, int
                   int64_t nlist, const int32_t *els, double *elmats, int32_t *npts, void *stream);
 int ngsx_elvec_h1(const ngsx_mesh *mesh, const double *lset_v, int fe_order, int dt, int intorder, const ngsx_poly *h_f,
                   int64_t nlist, const int32_t *els, double *elvecs, int32_t *npts, void *stream);
+/* the same with a GridFunction factor in the coefficient (the reference evaluates an arbitrary CoefficientFunction tree per point,
+ * xfem/symboliccutlfi.cpp:120-140; a GridFunction CF is sum_i c_i phi_i at the point): f(x) = h_f(x) * gf(x), gf in H1 of order
+ * cf_order (1, 2) on the same mesh, coefficients cf_vec [ndof_cf], dof table cf_el2dof [ne][nd_cf].  H1 test space of order 1-2. */
+int ngsx_elvec_h1_cf(const ngsx_mesh *mesh, const double *lset_v, int fe_order, int dt, int intorder, const ngsx_poly *h_f, int cf_order,
+                     const int32_t *cf_el2dof, const double *cf_vec, int64_t nlist, const int32_t *els, double *elvecs, int32_t *npts, void *stream);
 
 /* ---- (d) CSR graph, colouring, scatter ------------------------------------------------------------------------- */
 typedef struct ngsx_graph ngsx_graph;   /* opaque, host object owning temporary device buffers */

@@ -893,6 +893,8 @@ __global__ void __launch_bounds__(WARPS * 32) k_elvec(ElvecArgs A, int64_t first
 struct ElvecTArgs {
   ElvecArgs E;
   int32_t *work; int32_t *work_count;
+  // optional GridFunction factor of the coefficient (H1 order CFO = 1, 2; orientation free): f(x) = poly(x) * sum_i c[dof_i] phi_i(x)
+  const double *cf_vec; const int32_t *cf_el2dof;
 };
 
 template <int DIM>
@@ -910,7 +912,19 @@ __device__ __forceinline__ double poly_at(const PolyDev2 &f, const double *lam, 
   return fx;
 }
 
-template <int DIM, int ORDER, bool CUTPASS>
+// value of the GridFunction factor at barycentrics lam (CFO = 0: no such factor)
+template <int DIM, int CFO>
+__device__ __forceinline__ double gf_factor(const double *cfl, const double *lam) {
+  if constexpr (CFO == 0) return 1.0;
+  else {
+    double v = 0.0;
+#pragma unroll
+    for (int i = 0; i < H1<DIM, CFO>::ND; i++) v += cfl[i] * h1_shape<DIM, CFO>(i, lam);
+    return v;
+  }
+}
+
+template <int DIM, int ORDER, bool CUTPASS, int CFO>
 __global__ void __launch_bounds__(128) k_elvec_t(ElvecTArgs T, int64_t nlist) {
   constexpr int ND = H1<DIM, ORDER>::ND;
   const ElvecArgs &A = T.E;
@@ -936,6 +950,12 @@ __global__ void __launch_bounds__(128) k_elvec_t(ElvecTArgs T, int64_t nlist) {
   double acc[ND];
 #pragma unroll
   for (int i = 0; i < ND; i++) acc[i] = 0.0;
+  constexpr int NCF = CFO == 0 ? 1 : H1<DIM, CFO == 0 ? 1 : CFO>::ND;
+  double cfl[NCF];
+  if constexpr (CFO > 0) {
+#pragma unroll
+    for (int i = 0; i < NCF; i++) cfl[i] = __ldg(T.cf_vec + __ldg(T.cf_el2dof + e * NCF + i));
+  }
   int np_used = 0;
   if constexpr (!CUTPASS) {
     if (dom == IF) {
@@ -951,7 +971,7 @@ __global__ void __launch_bounds__(128) k_elvec_t(ElvecTArgs T, int64_t nlist) {
 #pragma unroll
         for (int kk = 0; kk < DIM; kk++) last -= lam[kk];
         lam[DIM] = last;
-        const double fw = r.w * poly_at<DIM>(A.f, lam, p);
+        const double fw = r.w * poly_at<DIM>(A.f, lam, p) * gf_factor<DIM, CFO>(cfl, lam);
 #pragma unroll
         for (int i = 0; i < ND; i++) acc[i] += fw * h1_shape<DIM, ORDER>(i, lam);
       }
@@ -992,7 +1012,7 @@ __global__ void __launch_bounds__(128) k_elvec_t(ElvecTArgs T, int64_t nlist) {
 #pragma unroll
         for (int kk = 0; kk < DIM; kk++) last -= lam[kk];
         lam[DIM] = last;
-        const double fw = (r.w * sfac) * poly_at<DIM>(A.f, lam, p);
+        const double fw = (r.w * sfac) * poly_at<DIM>(A.f, lam, p) * gf_factor<DIM, CFO>(cfl, lam);
 #pragma unroll
         for (int i = 0; i < ND; i++) acc[i] += fw * h1_shape<DIM, ORDER>(i, lam);
       }
@@ -1010,17 +1030,17 @@ __global__ void __launch_bounds__(128) k_elvec_t(ElvecTArgs T, int64_t nlist) {
   if (A.npts) A.npts[k] = np_used;
 }
 
-template <int DIM, int ORDER>
-static int launch_elvec_t(const ElvecArgs &A, int64_t nlist, cudaStream_t st) {
+template <int DIM, int ORDER, int CFO = 0>
+static int launch_elvec_t(const ElvecArgs &A, int64_t nlist, cudaStream_t st, const double *cf_vec = nullptr, const int32_t *cf_el2dof = nullptr) {
   if (nlist >= (int64_t)INT32_MAX) { set_error("elvec_h1: more than 2^31 - 1 list entries"); return NGSX_ERR_ARG; }
   int32_t *work = nullptr;
   NGSX_CUDA(cudaMallocAsync(&work, (nlist + 1) * sizeof(int32_t), st));
-  ElvecTArgs T{A, work + 1, work};
+  ElvecTArgs T{A, work + 1, work, cf_vec, cf_el2dof};
   cudaError_t e0 = cudaMemsetAsync(work, 0, sizeof(int32_t), st);
   const size_t smem = (size_t)(A.nr_vol + A.nr_if) * 32 + 16 * sizeof(CutEntry);
   const unsigned nb = (unsigned)((nlist + 127) / 128);
-  k_elvec_t<DIM, ORDER, false><<<nb, 128, smem, st>>>(T, nlist);
-  k_elvec_t<DIM, ORDER, true><<<nb, 128, smem, st>>>(T, nlist);
+  k_elvec_t<DIM, ORDER, false, CFO><<<nb, 128, smem, st>>>(T, nlist);
+  k_elvec_t<DIM, ORDER, true, CFO><<<nb, 128, smem, st>>>(T, nlist);
   g_launches.fetch_add(2, std::memory_order_relaxed);
   cudaError_t e1 = cudaGetLastError();
   cudaFreeAsync(work, st);
@@ -1865,6 +1885,32 @@ int ngsx_elvec_h1(const ngsx_mesh *mesh, const double *lset_v, int fe_order, int
       case 32: return launch_elvec_t<3, 2>(A, nlist, as_stream(stream));
     }
   return dispatch_elvec<0>(A, fe_order, dd->sm_count, 1, nullptr, nlist, as_stream(stream));
+}
+
+int ngsx_elvec_h1_cf(const ngsx_mesh *mesh, const double *lset_v, int fe_order, int dt, int intorder, const ngsx_poly *h_f, int cf_order,
+                     const int32_t *cf_el2dof, const double *cf_vec, int64_t nlist, const int32_t *els, double *elvecs, int32_t *npts, void *stream) {
+  const DeviceData *dd; const double4 *rv, *ri; int nv, ni;
+  NGSX_REQUIRE((nlist == 0 || elvecs) && nlist >= 0 && cf_el2dof && cf_vec, "elvec_h1_cf: bad arguments");
+  if (int rc = fill_common(mesh, lset_v, fe_order, dt, intorder, &dd, &rv, &nv, &ri, &ni, 2)) return rc;
+  if (cf_order < 1 || cf_order > 2) { set_error("elvec_h1_cf: the coefficient GridFunction must be H1 of order 1 or 2"); return NGSX_ERR_UNSUPPORTED; }
+  ElvecArgs A{};
+  if (int rc = fill_poly(h_f, A.f)) return rc;
+  if (nlist == 0) return NGSX_OK;
+  A.M = *mesh; A.lset = lset_v; A.tab = dd->cut_table; A.dt = dt;
+  A.rule_vol = rv; A.nr_vol = nv; A.rule_if = ri; A.nr_if = ni;
+  A.els = els; A.group = 1; A.elvecs = elvecs; A.npts = npts;
+  cudaStream_t st = as_stream(stream);
+  switch (mesh->dim * 100 + fe_order * 10 + cf_order) {
+    case 211: return launch_elvec_t<2, 1, 1>(A, nlist, st, cf_vec, cf_el2dof);
+    case 212: return launch_elvec_t<2, 1, 2>(A, nlist, st, cf_vec, cf_el2dof);
+    case 221: return launch_elvec_t<2, 2, 1>(A, nlist, st, cf_vec, cf_el2dof);
+    case 222: return launch_elvec_t<2, 2, 2>(A, nlist, st, cf_vec, cf_el2dof);
+    case 311: return launch_elvec_t<3, 1, 1>(A, nlist, st, cf_vec, cf_el2dof);
+    case 312: return launch_elvec_t<3, 1, 2>(A, nlist, st, cf_vec, cf_el2dof);
+    case 321: return launch_elvec_t<3, 2, 1>(A, nlist, st, cf_vec, cf_el2dof);
+    case 322: return launch_elvec_t<3, 2, 2>(A, nlist, st, cf_vec, cf_el2dof);
+  }
+  return NGSX_ERR_UNSUPPORTED;
 }
 
 int ngsx_assemble_vec_h1(const ngsx_mesh *mesh, const double *lset_v, int fe_order, int dt, int intorder,

@@ -206,6 +206,32 @@ class GridFunction:
         shape = fes.ndof if getattr(fes, "dim", 1) == 1 else (fes.ndof, fes.dim)
         self.vec = torch.zeros(shape, dtype=torch.float64, device=fes.mesh.device)
 
+    # a scalar H1 GridFunction of order 1-2 as a factor of the coefficient of a linear form:  gf * v,  poly * gf * v
+    def __mul__(self, o):
+        if isinstance(o, Expr):
+            return o * self
+        if isinstance(o, (int, float, Poly)):
+            return _GfCoef(self, Poly.lift(o))
+        return NotImplemented
+
+    __rmul__ = __mul__
+
+
+class _GfCoef:
+    """poly * GridFunction: a coefficient waiting for its test function"""
+
+    def __init__(self, gf, poly):
+        self.gf, self.poly = gf, poly
+
+    def __mul__(self, o):
+        if isinstance(o, Expr):
+            return (o * self.poly) * self.gf if not set(self.poly.terms) <= {(0, 0, 0)} else (o * self.poly.terms.get((0, 0, 0), 0.0)) * self.gf
+        if isinstance(o, (int, float, Poly)):
+            return _GfCoef(self.gf, self.poly * Poly.lift(o))
+        return NotImplemented
+
+    __rmul__ = __mul__
+
 
 # ------------------------------------------------------------------------------------------------------------------
 # coefficient-function algebra: just enough to write the forms of the tutorials and polynomial integrands
@@ -368,9 +394,10 @@ class Expr:
     """sum of terms  coef * h^hpow * (product of atoms).  Atoms: u, v (scalars), gu, gv, n (vectors),
     and the contracted scalars gugv, gun, gvn; ju, jv = u - u.Other(), v - v.Other()."""
 
-    def __init__(self, terms: List[Tuple[float, int, Tuple[str, ...]]], poly: Optional[Poly] = None):
+    def __init__(self, terms: List[Tuple[float, int, Tuple[str, ...]]], poly: Optional[Poly] = None, gf=None):
         self.terms = terms
         self.poly = poly          # optional polynomial coefficient multiplying the whole expression (f * v)
+        self.gf = gf              # optional GridFunction factor of that coefficient (scalar H1, order 1-2)
 
     @staticmethod
     def atom(name):
@@ -427,11 +454,22 @@ class Expr:
         return a + "." + b
 
     def __mul__(self, o):
+        if isinstance(o, GridFunction):
+            if self.gf is not None or getattr(o.space, "dim", 1) != 1 or not isinstance(o.space, H1) or o.space.order not in (1, 2):
+                raise _lib.NgsxError(-2, "one scalar H1 GridFunction of order 1-2 may multiply a linear form f*v")
+            return Expr(list(self.terms), self.poly, o)
+        if isinstance(o, _GfCoef):
+            return o * self
         if isinstance(o, Poly) and not set(o.terms) <= {(0, 0, 0)}:
-            return Expr(list(self.terms), o if self.poly is None else self.poly * o)
+            return Expr(list(self.terms), o if self.poly is None else self.poly * o, self.gf)
         o = Expr.lift(o)
         if o is None:
             return NotImplemented
+        if self.gf is not None or o.gf is not None:
+            if o.terms and all(a == () and p == 0 for _, p, a in o.terms) and o.gf is None:      # scalar * (gf * v)
+                c = sum(cc for cc, _, _ in o.terms)
+                return Expr([(c * c1, p1, a1) for c1, p1, a1 in self.terms], self.poly, self.gf)
+            raise _lib.NgsxError(-2, "a GridFunction coefficient may only multiply a finished linear form f*v")
         if self.poly is not None or o.poly is not None:
             raise _lib.NgsxError(-2, "a polynomial coefficient may only multiply a finished linear form f*v")
         out = []

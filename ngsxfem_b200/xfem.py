@@ -472,6 +472,9 @@ class SymbolicCutLFI:
         self.poly = form.poly if form.poly is not None else Poly({(0, 0, 0): 1.0})
         self.coef = self.poly * self.blocks[0]
         self.has_x = self.blocks[1] != 0.0 or self.blocks[2] != 0.0
+        self.gf = getattr(form, "gf", None)                # GridFunction factor of the coefficient: f = poly * gf (ngsx_elvec_h1_cf)
+        if self.gf is not None and (self.has_x or deformation is not None):
+            raise NgsxError(-2, "a GridFunction coefficient is served for f*v on H1 (affine mesh); no CPU fallback")
 
     def intorder(self, fe_order):
         return self.force_intorder if self.force_intorder >= 0 else 2 * fe_order       # xfem/symboliccutlfi.cpp:85
@@ -1077,6 +1080,8 @@ class LinearForm:
         self.vec.zero_()
         for k, integ in enumerate(self.integrators):
             gfd = integ.deformation if getattr(integ, "deformation", None) is not None else fes.mesh.deformation
+            if getattr(integ, "gf", None) is not None and (gfd is not None or fes.order > 2 or integ.gf.space.mesh is not fes.mesh):
+                raise NgsxError(-2, "a GridFunction coefficient is served on affine meshes for H1 order 1-2 (same mesh); no CPU fallback")
             if gfd is not None:
                 self._assemble_deformed(integ, k, gfd)
                 if integ.has_x:
@@ -1086,8 +1091,14 @@ class LinearForm:
                 els, dofptr, pairs, elvecs = self._gather_plan(("h1", k), integ)
                 if els.numel():
                     poly = _poly_of(integ.coef)
-                    check(L.ngsx_elvec_h1(ctypes.byref(fes.mesh.c_struct()), _ptr(_lset_vec(integ.lset)), fes.order, integ.dt,
-                                          integ.intorder(fes.order), ctypes.byref(poly), els.numel(), _ptr(els), _ptr(elvecs), None, _stream()))
+                    if getattr(integ, "gf", None) is not None:
+                        cfs = integ.gf.space
+                        check(L.ngsx_elvec_h1_cf(ctypes.byref(fes.mesh.c_struct()), _ptr(_lset_vec(integ.lset)), fes.order, integ.dt,
+                                                 integ.intorder(fes.order), ctypes.byref(poly), cfs.order, _ptr(cfs.el2dof), _ptr(integ.gf.vec),
+                                                 els.numel(), _ptr(els), _ptr(elvecs), None, _stream()))
+                    else:
+                        check(L.ngsx_elvec_h1(ctypes.byref(fes.mesh.c_struct()), _ptr(_lset_vec(integ.lset)), fes.order, integ.dt,
+                                              integ.intorder(fes.order), ctypes.byref(poly), els.numel(), _ptr(els), _ptr(elvecs), None, _stream()))
                     check(L.ngsx_gather_vec(fes.ndof, _ptr(dofptr), _ptr(pairs), _ptr(elvecs), 1.0, 1, _ptr(self.vec), _stream()))
             if integ.has_x:
                 self._assemble_x(integ, k)

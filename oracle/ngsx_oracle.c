@@ -604,6 +604,33 @@ int orc_elvec_h1(int dim, int fe_order, const int *vnums, const double *pmat, co
   return np;
 }
 
+/* the same with a GridFunction factor in the coefficient: f(x) = poly(x) * gf(x).  The reference evaluates the CoefficientFunction tree
+ * per point (xfem/symboliccutlfi.cpp:120-140); a GridFunction CF on the element is  sum_i cf_local[i] phi_i  with the H1 shapes of its
+ * own order at the same reference point (NGS/comp/gridfunction.cpp GridFunctionCoefficientFunction::Evaluate). */
+int orc_elvec_h1_cf(int dim, int fe_order, const int *vnums, const double *pmat, const double *ls, int dt, int intorder,
+                    int nmono, const double *mono, int cf_order, const double *cf_local, double *elvec)
+{
+  static _Thread_local double pts[3*ORC_MAXPTS], w[ORC_MAXPTS];
+  int np = orc_cut_rule(dim, pmat, ls, dt, intorder, pts, w, ORC_MAXPTS);
+  int nd = orc_h1_ndof(dim, fe_order), ncf = orc_h1_ndof(dim, cf_order);
+  for (int i = 0; i < nd; i++) elvec[i] = 0;
+  if (np < 0) return np;
+  affine_t A;
+  affine_init(dim, pmat, &A);
+  double meas = fabs(A.det);
+  double shape[ORC_MAXND], cshape[ORC_MAXND], dref[ORC_MAXND*3], x[3];
+  for (int q = 0; q < np; q++) {
+    orc_h1_shape(dim, fe_order, vnums, pts + 3*q, shape, dref);
+    if (orc_h1_shape(dim, cf_order, vnums, pts + 3*q, cshape, dref) < 0) return ORC_UNSUP;
+    affine_map(&A, pts + 3*q, x);
+    double g = 0;
+    for (int i = 0; i < ncf; i++) g += cf_local[i] * cshape[i];
+    double pv = meas * w[q] * eval_mono(nmono, mono, x) * g;
+    for (int i = 0; i < nd; i++) elvec[i] += pv * shape[i];
+  }
+  return np;
+}
+
 /* ------------------------------------------------------------------ deformed (isoparametric) elements, SURVEY 8 f-4 */
 /* mesh.SetDeformation(gf) (NGS/comp/meshaccess.cpp ALE_ElementTransformation: point and Jacobian of the base
  * transformation plus the deformation field and its reference gradient) == FE_ElementTransformation with the H1 element of

@@ -50,6 +50,7 @@ def load():
     L.orc_h1_shape.argtypes = [c_int, c_int, ip, dp, dp, dp]
     L.orc_elmat_h1.argtypes = [c_int, c_int, ip, dp, dp, c_int, c_int, c_double, c_double, dp]
     L.orc_elvec_h1.argtypes = [c_int, c_int, ip, dp, dp, c_int, c_int, c_int, dp, dp]
+    L.orc_elvec_h1_cf.argtypes = [c_int, c_int, ip, dp, dp, c_int, c_int, c_int, dp, c_int, dp, dp]
     L.orc_interpolate_p1_clamp.argtypes = [c_i64, dp, c_double, dp]
     L.orc_cutinfo_mesh.argtypes = [c_int, c_i64, ip, dp, dp, bp, dp]
     L.orc_cutinfo_mesh.restype = c_i64
@@ -226,6 +227,15 @@ def elvec_h1(dim, fe_order, vnums, pmat, lset, dt, intorder, mono, impl="oracle"
     else:
         from . import refload
         n = refload.load().ref_elvec_h1(ET[dim], fe_order, P(vn, ip), P(pm), P(ls), dt, intorder, len(mo), P(mo), P(ev))
+    return n, ev
+
+
+def elvec_h1_cf(dim, fe_order, vnums, pmat, lset, dt, intorder, mono, cf_order, cf_local):
+    """element vector of (poly * gf) v: cf_local = the coefficient GridFunction's values on the element's dofs (H1 order cf_order)"""
+    nd = load().orc_h1_ndof(dim, fe_order)
+    ev = np.zeros(nd)
+    vn = _i(vnums); pm = _d(pmat); ls = _d(lset); mo = mono_array(mono); cl = _d(cf_local)
+    n = load().orc_elvec_h1_cf(dim, fe_order, P(vn, ip), P(pm), P(ls), dt, intorder, len(mo), P(mo), cf_order, P(cl), P(ev))
     return n, ev
 
 

@@ -1511,6 +1511,46 @@ def test_order3_tensor_core_kernel_against_fma_kernel(X, dim, nx):
         L.ngsx_debug_set_fast_path(1)
 
 
+@pytest.mark.parametrize("dim,fo,cfo", [(2, 1, 2), (2, 2, 1), (3, 2, 2), (3, 1, 1)])
+def test_linear_form_with_gridfunction_coefficient(X, dim, fo, cfo):
+    """right-hand side (poly * gf) v with gf a scalar H1 GridFunction of order cfo (general coefficient functions, xfem/symboliccutlfi.cpp:
+    120-140: the CF is evaluated per point; a GridFunction CF = sum_i c_i phi_i): ngsx_elvec_h1_cf + the per-dof gather against the
+    oracle (orc_elvec_h1_cf, pinned by exactness for polynomial data), all domains; unsupported combinations raise"""
+    from oracle import orc
+    ngs, xf = X.ngs, X.xfem
+    mesh = ngs.Mesh(X.meshes.MakeStructured2DMesh(9) if dim == 2 else X.meshes.MakeStructured3DMesh(4))
+    gf = ngs.GridFunction(ngs.H1(mesh, order=1))
+    xf.InterpolateToP1(ngs.SphereLevelset((0.5,) * dim, 0.36), gf)
+    Vh, Vc = ngs.H1(mesh, order=fo), ngs.H1(mesh, order=cfo)
+    v = Vh.TestFunction()
+    c = ngs.GridFunction(Vc)
+    c.vec.copy_(dev(np.random.default_rng(5 + dim).uniform(-1, 1, Vc.ndof)))
+    el2v, vert, ls = mesh.el2v.cpu().numpy(), mesh.vert.cpu().numpy(), gf.vec.cpu().numpy()
+    e2d, c2d, cv = Vh.el2dof.cpu().numpy(), Vc.el2dof.cpu().numpy(), c.vec.cpu().numpy()
+    for dt in (NEG, POS, IF):
+        for form, mono in ((c * v, [(1.0, 0, 0, 0)]), ((1.0 + 0.5 * ngs.x * ngs.y) * c * v, [(1.0, 0, 0, 0), (0.5, 1, 1, 0)]), (2.0 * (c * v), [(2.0, 0, 0, 0)])):
+            f = xf.LinearForm(Vh)
+            f += xf.SymbolicLFI(levelset_domain={"levelset": gf, "domain_type": dt}, form=form)
+            f.Assemble()
+            first = f.vec.clone()
+            f.Assemble()
+            assert torch.equal(first, f.vec)
+            want = np.zeros(Vh.ndof)
+            for e in range(mesh.ne):
+                n, ev = orc.elvec_h1_cf(dim, fo, el2v[e], vert[el2v[e]], ls[el2v[e]], dt, 2 * fo, mono, cfo, cv[c2d[e]])
+                if n > 0:
+                    np.add.at(want, e2d[e], ev)
+            assert np.abs(want).max() > 0
+            assert np.abs(f.vec.cpu().numpy() - want).max() <= RTOL * np.abs(want).max()
+    with pytest.raises(X.lib.NgsxError):
+        (c * v) * c                                                       # one GridFunction factor
+    with pytest.raises(X.lib.NgsxError):
+        V3 = ngs.H1(mesh, order=3)
+        g = xf.LinearForm(V3)
+        g += xf.SymbolicLFI(levelset_domain={"levelset": gf, "domain_type": NEG}, form=c * V3.TestFunction())
+        g.Assemble()
+
+
 def test_peer_exchange_single_rank(X):
     """the mailbox exchange of the Integrate() scalars (csrc/ngsx_peer.cu) with world = 1: the kernel publishes into its own mailbox,
     delivers the PREVIOUS step's totals, survives more steps than it has slots, and replays inside a CUDA graph (the step counter

@@ -234,3 +234,38 @@ def test_orth_cut_hex3d(domain, dim):
     vals = p1(lambda x, y, z: 1 - 2 * (x, y, z)[dim], np.array(HEX_V, dtype=float))
     n, _, w = qr.rule_untrafo_hex(vals, domain, 2)
     assert n > 0 and abs(w.sum() - {NEG: 0.5, POS: 0.5, IF: 1.0}[domain]) < 5e-15 * 9
+
+
+@pytest.mark.parametrize("dim", [2, 3])
+def test_elvec_with_gridfunction_coefficient_is_exact_for_polynomials(dim):
+    """orc_elvec_h1_cf (f = poly * GridFunction, the GridFunction evaluated as sum_i c_i phi_i like NGSolve's
+    GridFunctionCoefficientFunction): a P2 GridFunction that holds a quadratic polynomial exactly -- vertex values + hierarchical
+    edge coefficients c_e = -8 (f(mid) - (f(a) + f(b)) / 2), since phi_e(mid) = -1/8 (NGS/fem/recursive_pol.hpp:1372) -- reproduces the
+    element vector of the polynomial coefficient (itself pinned against the compiled reference) on cut and uncut elements"""
+    rng = np.random.default_rng(31 + dim)
+    edges = [(2, 0), (1, 2), (0, 1)] if dim == 2 else [(3, 0), (3, 1), (3, 2), (0, 1), (0, 2), (1, 2)]
+    f = (lambda X: 1.0 + X[..., 0] * X[..., 1] + 0.5 * X[..., -1] ** 2 - 0.3 * X[..., 0])
+    mono = [(1.0, 0, 0, 0), (1.0, 1, 1, 0), (-0.3, 1, 0, 0)] + ([(0.5, 0, 0, 2)] if dim == 3 else [(0.5, 0, 2, 0)])
+    nchk = 0
+    for trial in range(40):
+        pm = rng.uniform(-1, 1, size=(dim + 1, dim))
+        if abs(np.linalg.det((pm[:dim] - pm[dim]).T)) < 0.05:
+            continue
+        ls = rng.uniform(-1, 1, size=dim + 1) + (0.0 if trial % 3 else 2.0)
+        vn = np.arange(dim + 1, dtype=np.int32)
+        fv = f(pm)
+        cf2 = np.concatenate([fv, [-8.0 * (f(0.5 * (pm[a] + pm[b])) - 0.5 * (fv[a] + fv[b])) for a, b in edges]])
+        for dt in (0, 1, 2):
+            for fo in (1, 2):
+                n1, ref = orc.elvec_h1(dim, fo, vn, pm, ls, dt, 2 * fo + 2, mono)
+                n2, got = orc.elvec_h1_cf(dim, fo, vn, pm, ls, dt, 2 * fo + 2, [(1.0, 0, 0, 0)], 2, cf2)
+                assert max(n1, 0) == max(n2, 0)
+                if n1 > 0:
+                    nchk += 1
+                    assert np.abs(got - ref).max() <= 1e-13 * max(np.abs(ref).max(), 1e-3)
+                    # a P1 coefficient times a polynomial: (x) * (P1 holding 1 + 2y) against the product polynomial
+                    p1 = 1.0 + 2.0 * pm[:, 1]
+                    _, a1 = orc.elvec_h1_cf(dim, fo, vn, pm, ls, dt, 2 * fo + 2, [(1.0, 1, 0, 0)], 1, p1)
+                    _, a2 = orc.elvec_h1(dim, fo, vn, pm, ls, dt, 2 * fo + 2, [(1.0, 1, 0, 0), (2.0, 1, 1, 0)])
+                    assert np.abs(a1 - a2).max() <= 1e-13 * max(np.abs(a2).max(), 1e-3)
+    assert nchk > 60
