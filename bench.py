@@ -339,7 +339,7 @@ def run_b200(args):
             a.mat.vals.copy_(ref_vals)
             del wrote
             graph_timing = pworld == 1
-            graph_note = f"CUDA graph per rank (assembly chain + three forked sweep streams, order '{order_default}', sweeps {sweep_mode}), " + ("scalar exchange inside (peer mailboxes)" if peer is not None else "NCCL all-reduce outside")
+            graph_note = f"CUDA graph per rank (assembly chain + forked sweep streams, order '{order_default}', sweeps {sweep_mode}), " + ("scalar exchange inside (peer mailboxes)" if peer is not None else ("NCCL all-reduce outside" if world > 1 else "single GPU: no exchange"))
             del ref_vals
         except Exception as exc:                                         # capture unsupported on this driver: stay eager
             graph, graph_note, graph_timing = None, f"eager (graph capture failed: {type(exc).__name__}: {str(exc)[:200]})", False
