@@ -20,30 +20,48 @@ class PeerExchange:
         self.rank, self.world, self.device = rank, world, torch.device(device)
         self._L = L
         self.mailbox = ctypes.c_void_p()
-        handle = (ctypes.c_ubyte * 64)()
-        with torch.cuda.device(self.device):
-            check(L.ngsx_peer_alloc(world, ctypes.byref(self.mailbox), handle))
-        handles = [None] * world
-        if world > 1:
-            dist.all_gather_object(handles, bytes(handle), group=group)
         self._opened = []
-        ptrs = []
-        for r in range(world):
-            if r == rank:
-                ptrs.append(self.mailbox.value)
-                continue
-            p = ctypes.c_void_p()
-            buf = (ctypes.c_ubyte * 64).from_buffer_copy(handles[r])
+        handle = (ctypes.c_ubyte * 64)()
+        # every rank runs the same collectives whatever fails locally (a rank that raised early would leave the others waiting)
+        err = None
+        try:
             with torch.cuda.device(self.device):
-                check(L.ngsx_peer_open(buf, ctypes.byref(p)))
-            self._opened.append(p)
-            ptrs.append(p.value)
+                check(L.ngsx_peer_alloc(world, ctypes.byref(self.mailbox), handle))
+        except Exception as exc:                                                           # noqa: BLE001
+            err = exc
+        handles = [bytes(handle) if err is None else None]
+        if world > 1:
+            handles = [None] * world
+            dist.all_gather_object(handles, bytes(handle) if err is None else None, group=group)
+        ptrs = []
+        if err is None and all(h is not None for h in handles):
+            try:
+                for r in range(world):
+                    if r == rank:
+                        ptrs.append(self.mailbox.value)
+                        continue
+                    p = ctypes.c_void_p()
+                    buf = (ctypes.c_ubyte * 64).from_buffer_copy(handles[r])
+                    with torch.cuda.device(self.device):
+                        check(L.ngsx_peer_open(buf, ctypes.byref(p)))
+                    self._opened.append(p)
+                    ptrs.append(p.value)
+            except Exception as exc:                                                       # noqa: BLE001
+                err = exc
+        elif err is None:
+            err = NgsxError(-3, "a peer could not allocate / export its mailbox")
+        if world > 1:                                                                      # also the barrier: every mailbox is mapped before anyone publishes
+            ok = torch.tensor([0 if err is not None else 1], device=self.device)
+            dist.all_reduce(ok, op=dist.ReduceOp.MIN, group=group)
+            if int(ok.item()) == 0 and err is None:
+                err = NgsxError(-3, "a peer could not map the mailboxes (CUDA IPC)")
+        if err is not None:
+            self.close()
+            raise err
         self.peers = torch.tensor(ptrs, dtype=torch.int64, device=self.device)            # device array of the world mailbox addresses
         self.step = torch.zeros(1, dtype=torch.int64, device=self.device)
         self.prev = torch.zeros(MAXVALS, dtype=torch.float64, device=self.device)          # totals of the previous step
         self.last = torch.zeros(MAXVALS, dtype=torch.float64, device=self.device)
-        if world > 1:
-            dist.barrier(group=group)                                                     # every mailbox is mapped before anyone publishes
 
     def exchange(self, local: torch.Tensor) -> torch.Tensor:
         """publish this step's local sums (<= 4 doubles, device) to every rank; returns the buffer that holds the totals of the PREVIOUS
