@@ -358,6 +358,8 @@ def run_b200(args):
         else:
             w_out = step(None)
     if peer is not None:                                 # the mailbox totals against an NCCL all-reduce of the same local sums, once, untimed
+        if graph is None and w_out is None:
+            w_out = step(None)
         loc = torch.cat(g_out if graph is not None else w_out).clone()
         tot = peer.collect_last(2).clone()
         dist.all_reduce(loc)
