@@ -154,6 +154,10 @@ int ngsx_elvec_h1(const ngsx_mesh *mesh, const double *lset_v, int fe_order, int
  * cf_order (1, 2) on the same mesh, coefficients cf_vec [ndof_cf], dof table cf_el2dof [ne][nd_cf].  H1 test space of order 1-2. */
 int ngsx_elvec_h1_cf(const ngsx_mesh *mesh, const double *lset_v, int fe_order, int dt, int intorder, const ngsx_poly *h_f, int cf_order,
                      const int32_t *cf_el2dof, const double *cf_vec, int64_t nlist, const int32_t *els, double *elvecs, int32_t *npts, void *stream);
+/* IntegrateX (cutint/python_cutint.cpp:20-72) with a GridFunction factor in the integrand: out[0] = sum_e sum_q |det J_e| w_q h_f(x_q) gf(x_q),
+ * gf in H1 of order cf_order (1, 2).  Per-element shares written once each, then a reduction of fixed shape (bitwise reproducible). */
+int ngsx_integrate_cf(const ngsx_mesh *mesh, const double *lset_v, int dt, int order, const ngsx_poly *h_f, int cf_order, const int32_t *cf_el2dof,
+                      const double *cf_vec, double *out, void *stream);
 
 /* ---- (d) CSR graph, colouring, scatter ------------------------------------------------------------------------- */
 typedef struct ngsx_graph ngsx_graph;   /* opaque, host object owning temporary device buffers */

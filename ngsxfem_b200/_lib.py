@@ -65,6 +65,7 @@ SIGNATURES = {
                               c_void_p, c_void_p, c_void_p]),
     "ngsx_elvec_h1_cf": (c_int, [ctypes.POINTER(Mesh), c_void_p, c_int, c_int, c_int, ctypes.POINTER(Poly), c_int, c_void_p, c_void_p, c_i64,
                                  c_void_p, c_void_p, c_void_p, c_void_p]),
+    "ngsx_integrate_cf": (c_int, [ctypes.POINTER(Mesh), c_void_p, c_int, c_int, ctypes.POINTER(Poly), c_int, c_void_p, c_void_p, c_void_p, c_void_p]),
     "ngsx_gather_vec": (c_int, [c_i64, c_void_p, c_void_p, c_void_p, ctypes.c_double, c_int, c_void_p, c_void_p]),
     "ngsx_csr_graph_create": (c_int, [c_i64, ctypes.POINTER(c_void_p)]),
     "ngsx_csr_graph_set_lower": (c_int, [c_void_p, c_int]),

@@ -924,9 +924,19 @@ __device__ __forceinline__ double gf_factor(const double *cfl, const double *lam
   }
 }
 
+// test functions of the element vector; ORDER 0: the constant 1, i.e. the element's share of a scalar integral (Integrate)
+template <int DIM, int ORDER> struct TestFn {
+  static constexpr int ND = H1<DIM, ORDER == 0 ? 1 : ORDER>::ND;
+  static __device__ __forceinline__ double value(int i, const double *lam) { return h1_shape<DIM, ORDER == 0 ? 1 : ORDER>(i, lam); }
+};
+template <int DIM> struct TestFn<DIM, 0> {
+  static constexpr int ND = 1;
+  static __device__ __forceinline__ double value(int, const double *) { return 1.0; }
+};
+
 template <int DIM, int ORDER, bool CUTPASS, int CFO>
 __global__ void __launch_bounds__(128) k_elvec_t(ElvecTArgs T, int64_t nlist) {
-  constexpr int ND = H1<DIM, ORDER>::ND;
+  constexpr int ND = TestFn<DIM, ORDER>::ND;
   const ElvecArgs &A = T.E;
   extern __shared__ __align__(16) unsigned char smem_raw[];
   double4 *srule_vol = reinterpret_cast<double4 *>(smem_raw);
@@ -973,7 +983,7 @@ __global__ void __launch_bounds__(128) k_elvec_t(ElvecTArgs T, int64_t nlist) {
         lam[DIM] = last;
         const double fw = r.w * poly_at<DIM>(A.f, lam, p) * gf_factor<DIM, CFO>(cfl, lam);
 #pragma unroll
-        for (int i = 0; i < ND; i++) acc[i] += fw * h1_shape<DIM, ORDER>(i, lam);
+        for (int i = 0; i < ND; i++) acc[i] += fw * TestFn<DIM, ORDER>::value(i, lam);
       }
     }
   } else {
@@ -1014,7 +1024,7 @@ __global__ void __launch_bounds__(128) k_elvec_t(ElvecTArgs T, int64_t nlist) {
         lam[DIM] = last;
         const double fw = (r.w * sfac) * poly_at<DIM>(A.f, lam, p) * gf_factor<DIM, CFO>(cfl, lam);
 #pragma unroll
-        for (int i = 0; i < ND; i++) acc[i] += fw * h1_shape<DIM, ORDER>(i, lam);
+        for (int i = 0; i < ND; i++) acc[i] += fw * TestFn<DIM, ORDER>::value(i, lam);
       }
     }
   }
@@ -1028,6 +1038,32 @@ __global__ void __launch_bounds__(128) k_elvec_t(ElvecTArgs T, int64_t nlist) {
 #pragma unroll
   for (int i = 0; i < ND; i++) o[i] = meas * acc[i];
   if (A.npts) A.npts[k] = np_used;
+}
+
+// fixed-shape sum: block b adds its contiguous chunk (thread-strided, then a tree), one block adds the block sums
+__global__ void __launch_bounds__(256) k_sum_chunks(int64_t n, const double *__restrict__ in, double *__restrict__ partial) {
+  __shared__ double s[256];
+  const int64_t per = (n + gridDim.x - 1) / gridDim.x, lo = (int64_t)blockIdx.x * per, hi = min(n, lo + per);
+  double acc = 0.0;
+  for (int64_t i = lo + threadIdx.x; i < hi; i += 256) acc += in[i];
+  s[threadIdx.x] = acc;
+  __syncthreads();
+  for (int o = 128; o > 0; o >>= 1) {
+    if ((int)threadIdx.x < o) s[threadIdx.x] += s[threadIdx.x + o];
+    __syncthreads();
+  }
+  if (threadIdx.x == 0) partial[blockIdx.x] = s[0];
+}
+
+__global__ void __launch_bounds__(1024) k_sum_final(int64_t n, const double *__restrict__ partial, double *__restrict__ out) {
+  __shared__ double s[1024];
+  s[threadIdx.x] = (int64_t)threadIdx.x < n ? partial[threadIdx.x] : 0.0;
+  __syncthreads();
+  for (int o = 512; o > 0; o >>= 1) {
+    if ((int)threadIdx.x < o) s[threadIdx.x] += s[threadIdx.x + o];
+    __syncthreads();
+  }
+  if (threadIdx.x == 0) out[0] = s[0];
 }
 
 template <int DIM, int ORDER, int CFO = 0>
@@ -1911,6 +1947,44 @@ int ngsx_elvec_h1_cf(const ngsx_mesh *mesh, const double *lset_v, int fe_order, 
     case 322: return launch_elvec_t<3, 2, 2>(A, nlist, st, cf_vec, cf_el2dof);
   }
   return NGSX_ERR_UNSUPPORTED;
+}
+
+int ngsx_integrate_cf(const ngsx_mesh *mesh, const double *lset_v, int dt, int order, const ngsx_poly *h_f, int cf_order, const int32_t *cf_el2dof,
+                      const double *cf_vec, double *out, void *stream) {
+  const DeviceData *dd; const double4 *rv, *ri; int nv, ni;
+  NGSX_REQUIRE(out && cf_el2dof && cf_vec, "integrate_cf: bad arguments");
+  if (int rc = fill_common(mesh, lset_v, 1, dt, order, &dd, &rv, &nv, &ri, &ni, 2)) return rc;
+  if (cf_order < 1 || cf_order > 2) { set_error("integrate_cf: the integrand GridFunction must be H1 of order 1 or 2"); return NGSX_ERR_UNSUPPORTED; }
+  ElvecArgs A{};
+  if (int rc = fill_poly(h_f, A.f)) return rc;
+  cudaStream_t st = as_stream(stream);
+  const int64_t ne = mesh->ne;
+  if (ne == 0) { NGSX_CUDA(cudaMemsetAsync(out, 0, sizeof(double), st)); return NGSX_OK; }
+  // per-element shares (every entry written once, at its own place), then a reduction of fixed shape: bitwise reproducible
+  const int64_t nmid = std::min<int64_t>((ne + 255) / 256, 1024);
+  double *vals = nullptr;
+  NGSX_CUDA(cudaMallocAsync(&vals, (size_t)(ne + nmid) * sizeof(double), st));
+  A.M = *mesh; A.lset = lset_v; A.tab = dd->cut_table; A.dt = dt;
+  A.rule_vol = rv; A.nr_vol = nv; A.rule_if = ri; A.nr_if = ni;
+  A.els = nullptr; A.group = 1; A.elvecs = vals; A.npts = nullptr;
+  int rc = NGSX_ERR_UNSUPPORTED;
+  switch (mesh->dim * 10 + cf_order) {
+    case 21: rc = launch_elvec_t<2, 0, 1>(A, ne, st, cf_vec, cf_el2dof); break;
+    case 22: rc = launch_elvec_t<2, 0, 2>(A, ne, st, cf_vec, cf_el2dof); break;
+    case 31: rc = launch_elvec_t<3, 0, 1>(A, ne, st, cf_vec, cf_el2dof); break;
+    case 32: rc = launch_elvec_t<3, 0, 2>(A, ne, st, cf_vec, cf_el2dof); break;
+  }
+  cudaError_t e1 = cudaSuccess;
+  if (rc == NGSX_OK) {
+    k_sum_chunks<<<(unsigned)nmid, 256, 0, st>>>(ne, vals, vals + ne);
+    k_sum_final<<<1, 1024, 0, st>>>(nmid, vals + ne, out);
+    g_launches.fetch_add(2, std::memory_order_relaxed);
+    e1 = cudaGetLastError();
+  }
+  cudaFreeAsync(vals, st);
+  if (rc) return rc;
+  NGSX_CUDA(e1);
+  return NGSX_OK;
 }
 
 int ngsx_assemble_vec_h1(const ngsx_mesh *mesh, const double *lset_v, int fe_order, int dt, int intorder,

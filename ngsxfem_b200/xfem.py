@@ -267,6 +267,17 @@ def IntegrateX(lset, mesh: Mesh, cf=None, order: int = 5, domain_type=IF, subdiv
         return spacetime.integrate(lset, mesh, cf, order, domain_type, time_order, sync)
     lv = _lset_vec(lset)
     out = torch.zeros(1, dtype=torch.float64, device=mesh.device)
+    from .ngs import _GfCoef
+    if isinstance(cf, (GridFunction, _GfCoef)):                      # integrand = polynomial x H1 GridFunction (order 1-2), evaluated per point
+        gfc, pol = (cf, 1.0) if isinstance(cf, GridFunction) else (cf.gf, cf.poly)
+        cfs = gfc.space
+        if getattr(mesh, "tensor", False) or mesh.c_deformation() is not None or not isinstance(cfs, H1) or getattr(cfs, "dim", 1) != 1 or \
+                cfs.order not in (1, 2) or cfs.mesh is not mesh:
+            raise NgsxError(-2, "a GridFunction integrand is served on affine simplex meshes for scalar H1 of order 1-2 (same mesh); no CPU fallback")
+        poly = _poly_of(pol)
+        check(_lib_().ngsx_integrate_cf(ctypes.byref(mesh.c_struct()), _ptr(lv), int(domain_type), order, ctypes.byref(poly), cfs.order,
+                                        _ptr(cfs.el2dof), _ptr(gfc.vec), _ptr(out), _stream()))
+        return float(out.item()) if sync else out
     poly = _poly_of(cf)
     if getattr(mesh, "tensor", False):                               # quadrilaterals / hexahedra (row f-5)
         if quad_dir_policy != OPTIMAL:

@@ -1551,6 +1551,45 @@ def test_linear_form_with_gridfunction_coefficient(X, dim, fo, cfo):
         g.Assemble()
 
 
+@pytest.mark.parametrize("dim,cfo", [(2, 1), (2, 2), (3, 1), (3, 2)])
+def test_integrate_with_gridfunction_integrand(X, dim, cfo):
+    """Integrate(cf = polynomial x GridFunction): ngsx_integrate_cf against the oracle -- the P1 test functions are a partition of unity,
+    so the integral is the sum of the entries of orc_elvec_h1_cf at fe_order 1 -- and, for a P2 GridFunction holding a quadratic
+    exactly, against the polynomial path of ngsx_integrate; bitwise reproducible"""
+    from oracle import orc
+    ngs, xf = X.ngs, X.xfem
+    mesh = ngs.Mesh(X.meshes.MakeStructured2DMesh(8) if dim == 2 else X.meshes.MakeStructured3DMesh(4))
+    gf = ngs.GridFunction(ngs.H1(mesh, order=1))
+    xf.InterpolateToP1(ngs.SphereLevelset((0.5,) * dim, 0.36), gf)
+    Vc = ngs.H1(mesh, order=cfo)
+    c = ngs.GridFunction(Vc)
+    c.vec.copy_(dev(np.random.default_rng(9 + dim).uniform(-1, 1, Vc.ndof)))
+    el2v, vert, ls = mesh.el2v.cpu().numpy(), mesh.vert.cpu().numpy(), gf.vec.cpu().numpy()
+    c2d, cv = Vc.el2dof.cpu().numpy(), c.vec.cpu().numpy()
+    for dt in (NEG, POS, IF):
+        for cf, mono in ((c, [(1.0, 0, 0, 0)]), ((1.0 + 0.5 * ngs.x * ngs.y) * c, [(1.0, 0, 0, 0), (0.5, 1, 1, 0)])):
+            got = xf.Integrate(levelset_domain={"levelset": gf, "domain_type": dt}, cf=cf, mesh=mesh, order=3)
+            assert got == xf.Integrate(levelset_domain={"levelset": gf, "domain_type": dt}, cf=cf, mesh=mesh, order=3)
+            want = 0.0
+            for e in range(mesh.ne):
+                n, ev = orc.elvec_h1_cf(dim, 1, el2v[e], vert[el2v[e]], ls[el2v[e]], dt, 3, mono, cfo, cv[c2d[e]])
+                if n > 0:
+                    want += ev.sum()
+            assert abs(got - want) <= 1e-12 * max(abs(want), 1e-3)
+    if cfo == 2:                                                       # exactness: the hierarchical P2 interpolant of a quadratic
+        f = lambda P: 1.0 + P[..., 0] * P[..., 1] - 0.3 * P[..., 0] ** 2
+        e2v, _ = mesh.edges()
+        V = mesh.vert
+        fv = f(V)
+        a, b = e2v[:, 0].long(), e2v[:, 1].long()
+        c.vec[:mesh.nv] = fv
+        c.vec[mesh.nv:] = -8.0 * (f(0.5 * (V[a] + V[b])) - 0.5 * (fv[a] + fv[b]))
+        for dt in (NEG, IF):
+            got = xf.Integrate(levelset_domain={"levelset": gf, "domain_type": dt}, cf=c, mesh=mesh, order=4)
+            ref = xf.Integrate(levelset_domain={"levelset": gf, "domain_type": dt}, cf=1.0 + ngs.x * ngs.y - 0.3 * ngs.x * ngs.x, mesh=mesh, order=4)
+            assert abs(got - ref) <= 1e-12 * abs(ref)
+
+
 def test_peer_exchange_single_rank(X):
     """the mailbox exchange of the Integrate() scalars (csrc/ngsx_peer.cu) with world = 1: the kernel publishes into its own mailbox,
     delivers the PREVIOUS step's totals, survives more steps than it has slots, and replays inside a CUDA graph (the step counter
