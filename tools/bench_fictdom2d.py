@@ -35,9 +35,8 @@ def main():
     lam = 10.0 * order * order
     a = xf.RestrictedBilinearForm(Vh, element_restriction=hasneg, facet_restriction=ba)
     a += xf.SymbolicBFI(levelset_domain={"levelset": gf, "domain_type": xf.NEG}, form=ngs.grad(u) * ngs.grad(v), definedonelements=hasneg)
-    if order <= 2:                                                   # Nitsche terms on the interface: orders 1-2 (ngsx_form_h1 on the fused row path)
-        a += xf.SymbolicBFI(levelset_domain={"levelset": gf, "domain_type": xf.IF},
-                            form=-(ngs.grad(u) * n) * v - (ngs.grad(v) * n) * u + (lam / h) * u * v, definedonelements=hasif)
+    a += xf.SymbolicBFI(levelset_domain={"levelset": gf, "domain_type": xf.IF},              # Nitsche terms on the interface
+                        form=-(ngs.grad(u) * n) * v - (ngs.grad(v) * n) * u + (lam / h) * u * v, definedonelements=hasif)
     a += xf.SymbolicFacetPatchBFI(form=0.1 * 1.0 / h * 1.0 / h * (u - u.Other()) * (v - v.Other()), skeleton=False, definedonelements=ba)
     ev = lambda: torch.cuda.Event(enable_timing=True)
     clocks = bench.ClockSampler(0)
@@ -59,7 +58,7 @@ def main():
     plan = a._plans[len(a.integrators) - 1]
     npatch = int(plan.els.shape[0])
     out = {"workload": f"configs[0] (fictdom_ghostpen.py) at H1 order {order}: 2D [-1,1]^2, ring level set, {mesh.ne} triangles, NEG stiffness"
-                       + (" + Nitsche IF terms" if order <= 2 else "") + " + 0.1/h^2 ghost-penalty facet patches, undeformed mesh",
+                       + " + Nitsche IF terms + 0.1/h^2 ghost-penalty facet patches, undeformed mesh",
            "ne": mesh.ne, "hasneg_elements": int(hasneg.NumSet()), "if_elements": int(hasif.NumSet()), "ghost_facets": npatch, "ndof": int(Vh.ndof),
            "nnz": int(a.mat.nnz), "first_assemble_s(symbolic+numeric)": round(setup_s, 2), "assemble_ms": ms,
            "hasneg_elements_per_s": int(hasneg.NumSet()) / (ms * 1e-3), "patches_per_s": npatch / (ms * 1e-3)}
