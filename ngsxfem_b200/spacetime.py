@@ -8,7 +8,7 @@ import torch
 
 from . import _lib
 from ._lib import NgsxError, check
-from .ngs import FESpace, GridFunction, H1, Poly, TPoly, _ptr, _stream
+from .ngs import Expr, FESpace, GridFunction, H1, Poly, TPoly, _ptr, _stream
 
 _S5, _S37, _S7 = 5.0 ** 0.5, (3.0 / 7.0) ** 0.5, 7.0 ** 0.5
 _NODES = {0: [0.0], 1: [0.0, 1.0], 2: [0.0, 0.5, 1.0],          # NodalTimeFE::CalcInterpolationPoints, spacetime/SpaceTimeFE.cpp:150-173
@@ -50,6 +50,15 @@ class SpaceTimeFESpace(FESpace):
 
     def TimeFE_nodes(self):
         return list(self.tfe.nodes)
+
+    def TrialFunction(self):
+        return Expr.atom("u")
+
+    def TestFunction(self):
+        return Expr.atom("v")
+
+    def TnT(self):
+        return self.TrialFunction(), self.TestFunction()
 
 
 def SpaceTimeInterpolateToP1(spacetime_cf, time=None, spacetime_gf: GridFunction = None, eps_perturbation: float = 0.0):
@@ -159,7 +168,8 @@ class SpaceTimeOperator:
     (GetGraph), owner-computes row plan, element blocks from ngsx_st_elmat_h1, gather without atomics (ngsx_assemble_csr_rows_mats).
     Pattern and plan are built once; Assemble() re-evaluates the blocks for the current level set."""
 
-    def __init__(self, fes: SpaceTimeFESpace, levelset, domain_type, c_mass=0.0, c_stiff=0.0, c_dt=0.0, order_space=None, order_time=None):
+    def __init__(self, fes: SpaceTimeFESpace, levelset, domain_type, c_mass=0.0, c_stiff=0.0, c_dt=0.0, order_space=None, order_time=None,
+                 share: "SpaceTimeOperator" = None):
         from .ngs import CSRMatrix
         L = _lib.load()
         self.fes, self.levelset, self.dt = fes, levelset, int(domain_type)
@@ -167,6 +177,11 @@ class SpaceTimeOperator:
         self.orders = (order_space, order_time)
         tab = fes.el2dof
         dev = fes.mesh.device
+        self._owner = share is None
+        if share is not None:                                # further integrators of one form: same pattern, plan and value array
+            self.mat, self.plan = share.mat, share.plan
+            self.blocks = torch.empty((tab.shape[0], fes.nd, fes.nd), dtype=torch.float64, device=dev)
+            return
         g = ctypes.c_void_p()
         check(L.ngsx_csr_graph_create(fes.ndof, ctypes.byref(g)))
         try:
@@ -186,15 +201,71 @@ class SpaceTimeOperator:
         self.plan = h
         self.blocks = torch.empty((tab.shape[0], fes.nd, fes.nd), dtype=torch.float64, device=dev)
 
-    def Assemble(self):
+    def Assemble(self, accumulate: bool = False):
         elmats(self.fes, self.levelset, self.dt, *self.coef, order_space=self.orders[0], order_time=self.orders[1], out=self.blocks)
-        check(_lib.load().ngsx_assemble_csr_rows_mats(self.plan, _ptr(self.blocks), 0, _ptr(self.mat.vals), _stream()))
+        check(_lib.load().ngsx_assemble_csr_rows_mats(self.plan, _ptr(self.blocks), 1 if accumulate else 0, _ptr(self.mat.vals), _stream()))
         return self
 
     def __del__(self):
         try:
-            if self.plan is not None:
+            if self.plan is not None and self._owner:
                 _lib.load().ngsx_rowplan_destroy(self.plan)
                 self.plan = None
         except Exception:
             pass
+
+
+def dt(e: Expr) -> Expr:
+    """spacetime/python_spacetime.cpp:194-249: derivative of a space-time trial function with respect to the REFERENCE time
+    (SpaceTimeFE::CalcDtShape).  The CUDA path serves dt(u) * v."""
+    (c, p, a), = e.terms
+    if a == ("u",):
+        return Expr([(c, p, ("dtu",))])
+    raise NgsxError(-2, "dt() of this expression is outside the CUDA path (served: dt(u) on the trial function)")
+
+
+class SymbolicSpaceTimeBFI:
+    """SymbolicBFI(levelset_domain=..., form=..., time_order=k) on a SpaceTimeFESpace: the space-time cut rule of order k in time
+    (cutint/xintegration.cpp:38-58) with the forms  c_m u v + c_s grad(u) grad(v) + c_t dt(u) v"""
+
+    def __init__(self, lset, domain_type, form: Expr, time_order: int, force_intorder: int = -1):
+        self.lset, self.dt, self.time_order, self.force_intorder = lset, int(domain_type), int(time_order), force_intorder
+        self.coef = [0.0, 0.0, 0.0]
+        names = {("u", "v"): 0, ("gugv",): 1, ("dtu", "v"): 2}
+        if not isinstance(form, Expr) or form.poly is not None or getattr(form, "gf", None) is not None:
+            raise NgsxError(-2, "space-time forms: c_m u v + c_s grad(u) grad(v) + c_t dt(u) v with constant coefficients; no CPU fallback")
+        for atoms, d in form.collect().items():
+            if atoms not in names or set(d) != {0}:
+                raise NgsxError(-2, f"space-time form term {atoms} is outside the CUDA path (served: u*v, grad(u)*grad(v), dt(u)*v)")
+            self.coef[names[atoms]] += d[0]
+
+
+class SpaceTimeBilinearForm:
+    """BilinearForm on a SpaceTimeFESpace: every integrator's blocks (ngsx_st_elmat_h1) gathered into one CSR matrix over the space-time
+    dofs (pattern and row plan built once, owner-computes gather, no atomics)"""
+
+    def __init__(self, space: SpaceTimeFESpace):
+        self.space = space
+        self.integrators = []
+        self._ops = []
+        self.mat = None
+
+    def __iadd__(self, integ):
+        if not isinstance(integ, SymbolicSpaceTimeBFI):
+            raise NgsxError(-2, "a BilinearForm on a SpaceTimeFESpace takes SymbolicBFI(levelset_domain=..., form=..., time_order=k) integrators")
+        self.integrators.append(integ)
+        return self
+
+    def Assemble(self, **_):
+        fes = self.space
+        while len(self._ops) < len(self.integrators):
+            i = self.integrators[len(self._ops)]
+            os_ = i.force_intorder if i.force_intorder >= 0 else None
+            op = SpaceTimeOperator(fes, i.lset, i.dt, *i.coef, order_space=os_, order_time=i.time_order, share=self._ops[0] if self._ops else None)
+            self._ops.append(op)
+        for k, op in enumerate(self._ops):
+            i = self.integrators[k]
+            op.levelset, op.dt, op.coef = i.lset, i.dt, tuple(i.coef)
+            op.Assemble(accumulate=k > 0)
+        self.mat = self._ops[0].mat if self._ops else None
+        return self

@@ -521,6 +521,10 @@ def SymbolicBFI(levelset_domain=None, *args, **kwargs):
     if "levelset" not in ld or "domain_type" not in ld:
         raise NgsxError(-1, "levelset_domain needs 'levelset' and 'domain_type'")
     form = kwargs.pop("form", args[0] if args else None)
+    time_order = kwargs.pop("time_order", ld.get("time_order", -1))
+    if time_order is not None and time_order >= 0:                  # space-time integrator (cutint/xintegration.cpp:38-58)
+        from . import spacetime
+        return spacetime.SymbolicSpaceTimeBFI(ld["levelset"], ld["domain_type"], form, time_order, ld.get("force_intorder", -1))
     return SymbolicCutBFI(lset=ld["levelset"], domain_type=ld["domain_type"], force_intorder=ld.get("force_intorder", -1),
                           subdivlvl=ld.get("subdivlvl", 0), quad_dir_policy=ld.get("quad_dir_policy", OPTIMAL), form=form, **kwargs)
 
@@ -600,6 +604,12 @@ class BilinearForm:
     The sparsity is the full element (and, with dgjumps, facet-patch) graph like NGSolve's GetGraph."""
     group_size = 6
     assembly = "rows"          # "rows": owner-computes row gather (default); "colored": colour-ordered scatter-add
+
+    def __new__(cls, space=None, *args, **kwargs):
+        from .spacetime import SpaceTimeBilinearForm, SpaceTimeFESpace
+        if cls is BilinearForm and isinstance(space, SpaceTimeFESpace):      # tensor-product space: blocks from ngsx_st_elmat_h1
+            return SpaceTimeBilinearForm(space)
+        return super().__new__(cls)
 
     def __init__(self, space: H1, symmetric: bool = False, check_unused: bool = False, **_):
         self.space = space
@@ -1171,5 +1181,5 @@ class LinearForm:
 
 # XFESpace and the sign-masked operators (xfem/python_xfem.cpp:321-448, python/__init__.py:22-105, 397-409)
 from .xfes import XFESpace, CutRatioGF, neg, pos, neg_grad, pos_grad, extend, extend_grad  # noqa: E402,F401
-from .spacetime import ScalarTimeFE, SpaceTimeFESpace, SpaceTimeInterpolateToP1  # noqa: E402,F401
+from .spacetime import ScalarTimeFE, SpaceTimeFESpace, SpaceTimeInterpolateToP1, dt  # noqa: E402,F401
 from .ngs import ReferenceTimeVariable  # noqa: E402,F401

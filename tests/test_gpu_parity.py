@@ -718,6 +718,34 @@ def test_spacetime_element_matrices_and_operator(X, dim, fo, tfe, tls):
 
 
 @pytest.mark.parametrize("dim", [2, 3])
+def test_spacetime_bilinear_form_surface(X, dim):
+    """the reference's spelling on a SpaceTimeFESpace: a = BilinearForm(st_fes); a += SymbolicBFI(levelset_domain=..., form=dt(u)*v + ...,
+    time_order=k) (python/__init__.py:107-192, spacetime/python_spacetime.cpp:194-249) -- two integrators summed into one CSR matrix,
+    against the oracle-tested SpaceTimeOperator of each; unsupported terms raise"""
+    from ngsxfem_b200 import spacetime
+    ngs, xf = X.ngs, X.xfem
+    mesh, _, gf = _st_setup(X, dim, 1, nx2=5, nx3=2)
+    fes = xf.SpaceTimeFESpace(ngs.H1(mesh, order=1), xf.ScalarTimeFE(1))
+    u, v = fes.TnT()
+    a = xf.BilinearForm(fes)
+    a += xf.SymbolicBFI(levelset_domain={"levelset": gf, "domain_type": NEG}, form=xf.dt(u) * v + 0.7 * ngs.grad(u) * ngs.grad(v), time_order=2)
+    a += xf.SymbolicBFI(levelset_domain={"levelset": gf, "domain_type": IF, "time_order": 2}, form=1.3 * u * v)
+    a.Assemble()
+    first = a.mat.vals.clone()
+    a.Assemble()
+    assert torch.equal(first, a.mat.vals)
+    o1 = spacetime.SpaceTimeOperator(fes, gf, NEG, 0.0, 0.7, 1.0, order_time=2).Assemble()
+    o2 = spacetime.SpaceTimeOperator(fes, gf, IF, 1.3, 0.0, 0.0, order_time=2).Assemble()
+    want = o1.mat.vals + o2.mat.vals
+    assert torch.equal(a.mat.colidx, o1.mat.colidx) and float(want.abs().max()) > 0
+    assert float((a.mat.vals - want).abs().max()) <= 1e-13 * float(want.abs().max())
+    with pytest.raises(X.lib.NgsxError):
+        xf.SymbolicBFI(levelset_domain={"levelset": gf, "domain_type": NEG}, form=xf.dt(u) * xf.dt(u), time_order=1)
+    with pytest.raises(X.lib.NgsxError):
+        xf.dt(v)
+
+
+@pytest.mark.parametrize("dim", [2, 3])
 def test_spacetime_cutinfo(X, dim):
     """f-3: CutInfo.Update(levelset, time_order) -- element classes of the space-time prisms (xfem/cutinfo.cpp:79-111 with the
     space-time rules) against the oracle"""
