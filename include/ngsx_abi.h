@@ -147,6 +147,11 @@ int ngsx_rule_fill(const ngsx_mesh *mesh, const double *lset_v, int dt, int orde
  * intorder < 0: the reference's default 2*fe_order - (difforders) is NOT guessed here -- the caller passes it. */
 int ngsx_elmat_h1(const ngsx_mesh *mesh, const double *lset_v, int fe_order, int dt, int intorder, const ngsx_form_h1 *h_form,
                   int64_t nlist, const int32_t *els, double *elmats, int32_t *npts, void *stream);
+/* the same with a GridFunction factor multiplying the whole form (the reference evaluates the coefficient tree per point,
+ * xfem/symboliccutbfi.cpp:178-215): gf in H1 of order cf_order (1, 2) on the same mesh.  H1 trial / test order 1-2; every listed element
+ * goes through the quadrature (no constant-rule shortcut: the coefficient varies inside the element). */
+int ngsx_elmat_h1_cf(const ngsx_mesh *mesh, const double *lset_v, int fe_order, int dt, int intorder, const ngsx_form_h1 *h_form, int cf_order,
+                     const int32_t *cf_el2dof, const double *cf_vec, int64_t nlist, const int32_t *els, double *elmats, int32_t *npts, void *stream);
 int ngsx_elvec_h1(const ngsx_mesh *mesh, const double *lset_v, int fe_order, int dt, int intorder, const ngsx_poly *h_f,
                   int64_t nlist, const int32_t *els, double *elvecs, int32_t *npts, void *stream);
 /* the same with a GridFunction factor in the coefficient (the reference evaluates an arbitrary CoefficientFunction tree per point,

@@ -63,6 +63,8 @@ SIGNATURES = {
                               c_void_p, c_void_p, c_void_p]),
     "ngsx_elvec_h1": (c_int, [ctypes.POINTER(Mesh), c_void_p, c_int, c_int, c_int, ctypes.POINTER(Poly), c_i64, c_void_p,
                               c_void_p, c_void_p, c_void_p]),
+    "ngsx_elmat_h1_cf": (c_int, [ctypes.POINTER(Mesh), c_void_p, c_int, c_int, c_int, ctypes.POINTER(FormH1), c_int, c_void_p, c_void_p, c_i64,
+                                 c_void_p, c_void_p, c_void_p, c_void_p]),
     "ngsx_elvec_h1_cf": (c_int, [ctypes.POINTER(Mesh), c_void_p, c_int, c_int, c_int, ctypes.POINTER(Poly), c_int, c_void_p, c_void_p, c_i64,
                                  c_void_p, c_void_p, c_void_p, c_void_p]),
     "ngsx_integrate_cf": (c_int, [ctypes.POINTER(Mesh), c_void_p, c_int, c_int, ctypes.POINTER(Poly), c_int, c_void_p, c_void_p, c_void_p, c_void_p]),

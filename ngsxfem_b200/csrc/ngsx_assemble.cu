@@ -39,6 +39,7 @@ struct ElmatArgs {
   const int32_t *d_count;      // optional device-resident number of work items (overrides `count`)
   int group;                   // list entries per warp-sequential group
   int use_fast;                // constant-rule path for uncut elements
+  const double *cf_vec; const int32_t *cf_el2dof; int cf_order;   // optional GridFunction factor of the whole form (H1 order 1-2): quadrature on every element
   int32_t *work; int32_t *work_count;   // order 3, dense sink: pass 1 records the quadrature-path entries here, pass 2 walks them (output at the entry)
   // sinks
   double *elmats; int32_t *npts;          // dense
@@ -112,7 +113,7 @@ __global__ void __launch_bounds__(WARPS * 32) k_elmat(ElmatArgs A, int64_t first
   for (int i = threadIdx.x; i < A.nr_if; i += blockDim.x) srule_if[i] = A.rule_if[i];
   if (threadIdx.x < 16) lut[threadIdx.x] = A.tab->e[DIM - 2][A.dt][threadIdx.x];
   __syncthreads();
-  const bool fast = A.use_fast && A.dt != IF && ORDER < 3;      // order 3: the edge functions depend on the element's vertex numbers
+  const bool fast = A.use_fast && A.dt != IF && ORDER < 3 && !A.cf_vec;      // order 3: the edge functions depend on the element's vertex numbers
   if (fast) {
     double glr[DIM + 1][DIM];                      // reference gradients of the barycentrics
 #pragma unroll
@@ -271,7 +272,19 @@ __global__ void __launch_bounds__(WARPS * 32) k_elmat(ElmatArgs A, int64_t first
                   h1_shape_grad<DIM, ORDER>(i, lam, gl, sv, gv, orient);
                   stage[lane * ND + i] = make_double4(sv, gv[0], gv[1], DIM == 3 ? gv[DIM - 1] : 0.0);
                 }
-                facq[lane] = meas * (r.w * sfac * scale);
+                double gfv = 1.0;
+                if (A.cf_vec) {                                  // GridFunction factor at the point: sum_i c_i phi_i (orientation-free orders 1, 2)
+                  gfv = 0.0;
+                  const int32_t *cd = A.cf_el2dof + e * (A.cf_order == 1 ? DIM + 1 : H1<DIM, 2>::ND);
+                  if (A.cf_order == 1) {
+#pragma unroll
+                    for (int i = 0; i <= DIM; i++) gfv += __ldg(A.cf_vec + __ldg(cd + i)) * h1_shape<DIM, 1>(i, lam);
+                  } else {
+#pragma unroll
+                    for (int i = 0; i < H1<DIM, 2>::ND; i++) gfv += __ldg(A.cf_vec + __ldg(cd + i)) * h1_shape<DIM, 2>(i, lam);
+                  }
+                }
+                facq[lane] = meas * (r.w * sfac * scale) * gfv;
               }
               __syncwarp();
               for (int q = 0; q < nq; q++) {
@@ -1807,6 +1820,23 @@ int ngsx_elmat_h1(const ngsx_mesh *mesh, const double *lset_v, int fe_order, int
   A.els = els; A.group = 1; A.use_fast = g_use_fast && h_form->c_nitsche == 0.0 && h_form->c_dndn == 0.0;
   A.elmats = elmats; A.npts = npts;
   if (take_packed_output()) { set_error("elmat_h1: packed output is not served by this entry point (measured for order 3: the scattered 160-byte row stores cost the producer more than the packed gather saves)"); return NGSX_ERR_UNSUPPORTED; }
+  return dispatch_elmat<0>(A, fe_order, dd->sm_count, 1, nullptr, nlist, as_stream(stream));
+}
+
+int ngsx_elmat_h1_cf(const ngsx_mesh *mesh, const double *lset_v, int fe_order, int dt, int intorder, const ngsx_form_h1 *h_form, int cf_order,
+                     const int32_t *cf_el2dof, const double *cf_vec, int64_t nlist, const int32_t *els, double *elmats, int32_t *npts, void *stream) {
+  const DeviceData *dd; const double4 *rv, *ri; int nv, ni;
+  NGSX_REQUIRE(h_form && (nlist == 0 || elmats) && nlist >= 0 && cf_el2dof && cf_vec, "elmat_h1_cf: bad arguments");
+  if (int rc = fill_common(mesh, lset_v, fe_order, dt, intorder, &dd, &rv, &nv, &ri, &ni, 2)) return rc;
+  if (cf_order < 1 || cf_order > 2) { set_error("elmat_h1_cf: the coefficient GridFunction must be H1 of order 1 or 2"); return NGSX_ERR_UNSUPPORTED; }
+  if (nlist == 0) return NGSX_OK;
+  ElmatArgs A{};
+  A.M = *mesh; A.lset = lset_v; A.tab = dd->cut_table; A.dt = dt;
+  A.rule_vol = rv; A.nr_vol = nv; A.rule_if = ri; A.nr_if = ni;
+  fill_form(h_form, A.form);
+  A.els = els; A.group = 1; A.use_fast = 0;
+  A.elmats = elmats; A.npts = npts;
+  A.cf_vec = cf_vec; A.cf_el2dof = cf_el2dof; A.cf_order = cf_order;
   return dispatch_elmat<0>(A, fe_order, dd->sm_count, 1, nullptr, nlist, as_stream(stream));
 }
 

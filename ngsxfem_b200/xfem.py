@@ -401,8 +401,11 @@ class SymbolicCutBFI:
         self.lset, self.dt, self.force_intorder, self.definedonelements = lset, int(domain_type), force_intorder, definedonelements
         self.deformation = deformation                     # bfi->SetDeformation (xfem/python_xfem.cpp:512-513); None: the mesh's
         self.xterms = None
+        self.gf = getattr(form, "gf", None)                # GridFunction factor of the whole form (ngsx_elmat_h1_cf)
         from . import xfes
         if xfes.has_x_atoms(form):
+            if self.gf is not None:
+                raise NgsxError(-2, "a GridFunction coefficient on the compound space is outside the CUDA path")
             self._init_x(form, xfes)
             return
         terms = form.collect()
@@ -853,10 +856,11 @@ class BilinearForm:
         for k, integ in enumerate(self.integrators):
             plan = plans[k]
             if self.symmetric and not (isinstance(plan, _RowPlan) and isinstance(integ, SymbolicCutBFI) and integ.xterms is None and
+                                       getattr(integ, "gf", None) is None and
                                        self._deformation_of(integ) is None and fes.order < 3 and self._h1 is fes):
                 raise NgsxError(-2, "symmetric=True is served by the fused H1 row path (SymbolicCutBFI, orders 1-2, affine mesh); no CPU fallback")
             plain_rows = isinstance(plan, _RowPlan) and not isinstance(integ, SymbolicFacetPatchBFI) and integ.xterms is None and \
-                self._deformation_of(integ) is None and fes.order < 3
+                self._deformation_of(integ) is None and fes.order < 3 and getattr(integ, "gf", None) is None
             if gather_after is not None and not plain_rows:
                 # only the fused H1 row path can hold back its gather alone (ngsx_set_gather_wait_event); every other producer
                 # honours the event by waiting for it on the stream before it starts
@@ -866,6 +870,19 @@ class BilinearForm:
                 self._assemble_facetpatch(integ, plan)
             elif integ.xterms is not None:
                 x_blocks += self._assemble_x(integ, plan, k, x_blocks)
+            elif isinstance(plan, _RowPlan) and getattr(integ, "gf", None) is not None:
+                # a GridFunction factor in the form: the coefficient varies inside the element, every listed element goes through the
+                # quadrature kernel (dense blocks), then the owner-computes gather
+                cfs = integ.gf.space
+                if self._deformation_of(integ) is not None or fes.order >= 3 or cfs.mesh is not fes.mesh:
+                    raise NgsxError(-2, "a GridFunction coefficient is served on affine meshes for H1 order 1-2 (same mesh); no CPU fallback")
+                lv = _lset_vec(integ.lset)
+                n = plan.els.numel()
+                if getattr(plan, "mats", None) is None:
+                    plan.mats = torch.empty((n, fes.nd * fes.nd), dtype=torch.float64, device=fes.mesh.device)
+                check(L.ngsx_elmat_h1_cf(mesh_c, _ptr(lv), fes.order, integ.dt, integ.intorder(fes.order), ctypes.byref(integ.form), cfs.order,
+                                         _ptr(cfs.el2dof), _ptr(integ.gf.vec), n, _ptr(plan.els), _ptr(plan.mats), None, _stream()))
+                check(L.ngsx_assemble_csr_rows_mats(plan.handle, _ptr(plan.mats), 0 if overwrite else 1, _ptr(self.mat.vals), _stream()))
             elif isinstance(plan, _RowPlan) and (self._deformation_of(integ) is not None or fes.order >= 3):
                 # deformed elements (row f-4: per-point geometry) and H1 order 3 (orientation-dependent edge functions: no shared
                 # constant-rule table): dense blocks of the listed elements, then the owner-computes gather (each CSR value
@@ -900,6 +917,8 @@ class BilinearForm:
                                                   _ptr(self.mat.vals), _ptr(self._err[k]), _stream()))
                 self._err_armed = True
             elif isinstance(integ, SymbolicCutBFI):
+                if getattr(integ, "gf", None) is not None:
+                    raise NgsxError(-2, "a GridFunction coefficient is served by the row gather (assembly = 'rows'); no CPU fallback")
                 lv = _lset_vec(integ.lset)
                 check(L.ngsx_assemble_csr_h1(mesh_c, _ptr(lv), fes.order, integ.dt, integ.intorder(fes.order), ctypes.byref(integ.form),
                                              plan.els.numel(), _ptr(plan.els), _ptr(plan.slots), plan.ncolors, plan.h_color_ptr,
@@ -1006,6 +1025,8 @@ class BilinearForm:
     def elmats(self, k: int = 0):
         """dense element matrices of integrator k for its active elements (the per-element view CalcElementMatrixAdd would serve)"""
         integ, fes, L = self.integrators[k], self.space, _lib_()
+        if getattr(integ, "gf", None) is not None:
+            raise NgsxError(-2, "elmats(): integrators with a GridFunction coefficient are served through Assemble()")
         els = self._active_elements(integ).to(torch.int32).contiguous()
         out = torch.empty((els.numel(), fes.nd, fes.nd), dtype=torch.float64, device=fes.mesh.device)
         npts = torch.empty(els.numel(), dtype=torch.int32, device=fes.mesh.device)

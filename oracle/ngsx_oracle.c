@@ -582,6 +582,42 @@ int orc_elmat_h1(int dim, int fe_order, const int *vnums, const double *pmat, co
   return np;
 }
 
+/* T_CalcElementMatrixAdd with a GridFunction coefficient multiplying the form: the reference evaluates the CoefficientFunction tree per point
+ * (xfem/symboliccutbfi.cpp:178-215); a GridFunction CF is  sum_i cf_local[i] phi_i  with the H1 shapes of its own order. */
+int orc_elmat_h1_cf(int dim, int fe_order, const int *vnums, const double *pmat, const double *ls, int dt, int intorder,
+                    double c_mass, double c_stiff, int cf_order, const double *cf_local, double *elmat)
+{
+  static _Thread_local double pts[3*ORC_MAXPTS], w[ORC_MAXPTS];
+  int np = orc_cut_rule(dim, pmat, ls, dt, intorder, pts, w, ORC_MAXPTS);
+  int nd = orc_h1_ndof(dim, fe_order), ncf = orc_h1_ndof(dim, cf_order);
+  for (int i = 0; i < nd*nd; i++) elmat[i] = 0;
+  if (np < 0) return np;
+  affine_t A;
+  affine_init(dim, pmat, &A);
+  double meas = fabs(A.det);
+  double shape[ORC_MAXND], cshape[ORC_MAXND], dref[ORC_MAXND*3], cdref[ORC_MAXND*3], dphys[ORC_MAXND*3];
+  for (int q = 0; q < np; q++) {
+    if (orc_h1_shape(dim, fe_order, vnums, pts + 3*q, shape, dref) < 0) return ORC_UNSUP;
+    if (orc_h1_shape(dim, cf_order, vnums, pts + 3*q, cshape, cdref) < 0) return ORC_UNSUP;
+    double g = 0;
+    for (int i = 0; i < ncf; i++) g += cf_local[i] * cshape[i];
+    for (int i = 0; i < nd; i++)
+      for (int d = 0; d < dim; d++) {
+        double v = 0;
+        for (int k = 0; k < dim; k++) v += dref[i*dim + k] * A.Jinv[k][d];
+        dphys[i*dim + d] = v;
+      }
+    double fac = meas * w[q] * g;
+    for (int i = 0; i < nd; i++)
+      for (int j = 0; j < nd; j++) {
+        double gg = 0;
+        for (int d = 0; d < dim; d++) gg += dphys[i*dim + d] * dphys[j*dim + d];
+        elmat[i*nd + j] += fac * (c_stiff * gg + c_mass * shape[i] * shape[j]);
+      }
+  }
+  return np;
+}
+
 /* xfem/symboliccutlfi.cpp:52-158 T_CalcElementVector, f = sum_m c_m x^a y^b z^c */
 int orc_elvec_h1(int dim, int fe_order, const int *vnums, const double *pmat, const double *ls, int dt, int intorder,
                  int nmono, const double *mono, double *elvec)

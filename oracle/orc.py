@@ -50,6 +50,7 @@ def load():
     L.orc_h1_shape.argtypes = [c_int, c_int, ip, dp, dp, dp]
     L.orc_elmat_h1.argtypes = [c_int, c_int, ip, dp, dp, c_int, c_int, c_double, c_double, dp]
     L.orc_elvec_h1.argtypes = [c_int, c_int, ip, dp, dp, c_int, c_int, c_int, dp, dp]
+    L.orc_elmat_h1_cf.argtypes = [c_int, c_int, ip, dp, dp, c_int, c_int, c_double, c_double, c_int, dp, dp]
     L.orc_elvec_h1_cf.argtypes = [c_int, c_int, ip, dp, dp, c_int, c_int, c_int, dp, c_int, dp, dp]
     L.orc_interpolate_p1_clamp.argtypes = [c_i64, dp, c_double, dp]
     L.orc_cutinfo_mesh.argtypes = [c_int, c_i64, ip, dp, dp, bp, dp]
@@ -228,6 +229,15 @@ def elvec_h1(dim, fe_order, vnums, pmat, lset, dt, intorder, mono, impl="oracle"
         from . import refload
         n = refload.load().ref_elvec_h1(ET[dim], fe_order, P(vn, ip), P(pm), P(ls), dt, intorder, len(mo), P(mo), P(ev))
     return n, ev
+
+
+def elmat_h1_cf(dim, fe_order, vnums, pmat, lset, dt, intorder, c_mass, c_stiff, cf_order, cf_local):
+    """element matrix of gf * (c_stiff grad(u) grad(v) + c_mass u v): cf_local = the coefficient GridFunction on the element's dofs"""
+    nd = load().orc_h1_ndof(dim, fe_order)
+    em = np.zeros((nd, nd))
+    vn = _i(vnums); pm = _d(pmat); ls = _d(lset); cl = _d(cf_local)
+    n = load().orc_elmat_h1_cf(dim, fe_order, P(vn, ip), P(pm), P(ls), dt, intorder, c_mass, c_stiff, cf_order, P(cl), P(em))
+    return n, em
 
 
 def elvec_h1_cf(dim, fe_order, vnums, pmat, lset, dt, intorder, mono, cf_order, cf_local):

@@ -1618,6 +1618,45 @@ def test_integrate_with_gridfunction_integrand(X, dim, cfo):
             assert abs(got - ref) <= 1e-12 * abs(ref)
 
 
+@pytest.mark.parametrize("dim,fo,cfo", [(2, 2, 1), (2, 1, 2), (3, 2, 2), (3, 1, 1)])
+def test_bilinear_form_with_gridfunction_coefficient(X, dim, fo, cfo):
+    """alpha_h * (c_s grad(u) grad(v) + c_m u v) with alpha_h a scalar H1 GridFunction (general coefficient functions,
+    xfem/symboliccutbfi.cpp:178-215): ngsx_elmat_h1_cf + the owner-computes gather against the oracle (orc_elmat_h1_cf, pinned to the
+    polynomial / element-vector paths by tests/test_oracle_kat.py), all domains, bitwise reproducible; unsupported combinations raise"""
+    from oracle import orc
+    ngs, xf = X.ngs, X.xfem
+    mesh = ngs.Mesh(X.meshes.MakeStructured2DMesh(8) if dim == 2 else X.meshes.MakeStructured3DMesh(4))
+    gf = ngs.GridFunction(ngs.H1(mesh, order=1))
+    xf.InterpolateToP1(ngs.SphereLevelset((0.5,) * dim, 0.36), gf)
+    Vh, Vc = ngs.H1(mesh, order=fo), ngs.H1(mesh, order=cfo)
+    u, v = Vh.TnT()
+    al = ngs.GridFunction(Vc)
+    al.vec.copy_(dev(1.5 + np.random.default_rng(3 + dim).uniform(-1, 1, Vc.ndof)))
+    el2v, vert, ls = mesh.el2v.cpu().numpy(), mesh.vert.cpu().numpy(), gf.vec.cpu().numpy()
+    e2d, c2d, cv = Vh.el2dof.cpu().numpy(), Vc.el2dof.cpu().numpy(), al.vec.cpu().numpy()
+    for dt in (NEG, POS, IF):
+        a = xf.BilinearForm(Vh)
+        a += xf.SymbolicBFI(levelset_domain={"levelset": gf, "domain_type": dt}, form=al * (0.7 * ngs.grad(u) * ngs.grad(v) + 1.3 * u * v))
+        a.Assemble()
+        first = a.mat.vals.clone()
+        a.mat.vals.fill_(float("nan"))
+        a.Assemble()
+        assert torch.equal(first, a.mat.vals)
+        dense = np.zeros((Vh.ndof, Vh.ndof))
+        io = a.integrators[0].intorder(fo)
+        for e in range(mesh.ne):
+            n, em = orc.elmat_h1_cf(dim, fo, el2v[e], vert[el2v[e]], ls[el2v[e]], dt, io, 1.3, 0.7, cfo, cv[c2d[e]])
+            if n > 0:
+                dense[np.ix_(e2d[e], e2d[e])] += em
+        A = a.mat.to_scipy().toarray()
+        assert np.abs(dense).max() > 0 and np.abs(A - dense).max() <= 1e-12 * np.abs(dense).max()
+    with pytest.raises(X.lib.NgsxError):
+        b = xf.BilinearForm(Vh)
+        b.assembly = "colored"
+        b += xf.SymbolicBFI(levelset_domain={"levelset": gf, "domain_type": NEG}, form=al * (u * v))
+        b.Assemble()
+
+
 def test_peer_exchange_single_rank(X):
     """the mailbox exchange of the Integrate() scalars (csrc/ngsx_peer.cu) with world = 1: the kernel publishes into its own mailbox,
     delivers the PREVIOUS step's totals, survives more steps than it has slots, and replays inside a CUDA graph (the step counter

@@ -269,3 +269,39 @@ def test_elvec_with_gridfunction_coefficient_is_exact_for_polynomials(dim):
                     _, a2 = orc.elvec_h1(dim, fo, vn, pm, ls, dt, 2 * fo + 2, [(1.0, 1, 0, 0), (2.0, 1, 1, 0)])
                     assert np.abs(a1 - a2).max() <= 1e-13 * max(np.abs(a2).max(), 1e-3)
     assert nchk > 60
+
+
+@pytest.mark.parametrize("dim", [2, 3])
+def test_elmat_with_gridfunction_coefficient_pins(dim):
+    """orc_elmat_h1_cf against pinned pieces: (a) constant coefficient c -> c * orc_elmat_h1; (b) mass form: the vertex functions are a
+    partition of unity, so the row sums over the vertex columns are the element vector of the same coefficient (orc_elvec_h1_cf);
+    (c) stiffness form applied to the linear function x_d: K_cf x_d = int gf d_d phi_i = the mass-form trick on the derivative side,
+    checked through symmetry and K_cf * 1 = 0"""
+    rng = np.random.default_rng(77 + dim)
+    nchk = 0
+    for trial in range(30):
+        pm = rng.uniform(-1, 1, size=(dim + 1, dim))
+        if abs(np.linalg.det((pm[:dim] - pm[dim]).T)) < 0.05:
+            continue
+        ls = rng.uniform(-1, 1, size=dim + 1) + (0.0 if trial % 3 else 2.0)
+        vn = np.arange(dim + 1, dtype=np.int32)
+        for fo in (1, 2):
+            for cfo in (1, 2):
+                ncf = orc.load().orc_h1_ndof(dim, cfo)
+                cl = rng.uniform(-1, 1, ncf)
+                for dt in (0, 1, 2):
+                    n0, base = orc.elmat_h1(dim, fo, vn, pm, ls, dt, 2 * fo, 1.3, 0.7)
+                    const = np.zeros(ncf); const[:dim + 1] = 2.5                  # hierarchical basis: the constant 2.5
+                    n1, em_c = orc.elmat_h1_cf(dim, fo, vn, pm, ls, dt, 2 * fo, 1.3, 0.7, cfo, const)
+                    assert max(n0, 0) == max(n1, 0)
+                    if n0 <= 0:
+                        continue
+                    nchk += 1
+                    assert np.abs(em_c - 2.5 * base).max() <= 1e-13 * np.abs(base).max()
+                    _, mass = orc.elmat_h1_cf(dim, fo, vn, pm, ls, dt, 2 * fo, 1.0, 0.0, cfo, cl)
+                    _, ev = orc.elvec_h1_cf(dim, fo, vn, pm, ls, dt, 2 * fo, [(1.0, 0, 0, 0)], cfo, cl)
+                    assert np.abs(mass[:, :dim + 1].sum(axis=1) - ev).max() <= 1e-13 * max(np.abs(ev).max(), 1e-3)
+                    _, stiff = orc.elmat_h1_cf(dim, fo, vn, pm, ls, dt, 2 * fo, 0.0, 1.0, cfo, cl)
+                    assert np.abs(stiff - stiff.T).max() <= 1e-13 * np.abs(stiff).max()
+                    assert np.abs(stiff[:, :dim + 1].sum(axis=1)).max() <= 1e-12 * np.abs(stiff).max()
+    assert nchk > 100
