@@ -368,9 +368,14 @@ __global__ void __launch_bounds__(1024) k_st_final(int64_t n, const double *__re
 // ---------------------------------------------------------------------------------------------------------------
 struct StForm { double cm, cs, ct; int ntd_fe; };
 
-template <int DIM, int ORDER>
+// NTDR > 0: the number of time dofs is the compile-time constant NTDR and the whole (NTDR NS)^2 block lives in registers (P1 in space x
+// time order 1: 36 / 64 doubles) -- the time outer products of a flush then cost no memory traffic; NTDR = 0: any time order, the flush
+// adds into the thread's block in global memory.
+template <int DIM, int ORDER, int NTDR = 0>
 struct StMatF {
   static constexpr int NS = H1<DIM, ORDER>::ND, NSYM = NS * (NS + 1) / 2;
+  static constexpr int NREG = NTDR > 0 ? NTDR * NS * NTDR * NS : 1;
+  double blk[NREG];
   const double (*gl)[DIM];
   double *out;                       // this entry's block, N x N, N = ntd_fe * NS
   StForm f;
@@ -384,18 +389,37 @@ struct StMatF {
     double tau[ST_MAXTD], dtau[ST_MAXTD];
     if (f.ntd_fe == 1) { tau[0] = 1.0; dtau[0] = 0.0; }
     else { st_lagrange(f.ntd_fe, tnodes, tcur, tau); st_dlagrange(f.ntd_fe, tnodes, tcur, dtau); }
-    const int N = f.ntd_fe * NS;
-    for (int j = 0; j < f.ntd_fe; j++)
-      for (int jp = 0; jp < f.ntd_fe; jp++) {
-        const double a = tau[j] * tau[jp], b = f.ct * tau[j] * dtau[jp];
-        int t = 0;
-        for (int i = 0; i < NS; i++)
-          for (int ip = i; ip < NS; ip++, t++) {
-            const double v = meas * (a * (f.cm * Sm[t] + f.cs * Ss[t]) + b * Sm[t]);
-            out[(j * NS + i) * N + jp * NS + ip] += v;
-            if (ip != i) out[(j * NS + ip) * N + jp * NS + i] += v;
-          }
-      }
+    if constexpr (NTDR > 0) {
+      constexpr int N = NTDR * NS;
+#pragma unroll
+      for (int j = 0; j < NTDR; j++)
+#pragma unroll
+        for (int jp = 0; jp < NTDR; jp++) {
+          const double a = tau[j] * tau[jp], b = f.ct * tau[j] * dtau[jp];
+          int t = 0;
+#pragma unroll
+          for (int i = 0; i < NS; i++)
+#pragma unroll
+            for (int ip = i; ip < NS; ip++, t++) {
+              const double v = meas * (a * (f.cm * Sm[t] + f.cs * Ss[t]) + b * Sm[t]);
+              blk[(j * NS + i) * N + jp * NS + ip] += v;
+              if (ip != i) blk[(j * NS + ip) * N + jp * NS + i] += v;
+            }
+        }
+    } else {
+      const int N = f.ntd_fe * NS;
+      for (int j = 0; j < f.ntd_fe; j++)
+        for (int jp = 0; jp < f.ntd_fe; jp++) {
+          const double a = tau[j] * tau[jp], b = f.ct * tau[j] * dtau[jp];
+          int t = 0;
+          for (int i = 0; i < NS; i++)
+            for (int ip = i; ip < NS; ip++, t++) {
+              const double v = meas * (a * (f.cm * Sm[t] + f.cs * Ss[t]) + b * Sm[t]);
+              out[(j * NS + i) * N + jp * NS + ip] += v;
+              if (ip != i) out[(j * NS + ip) * N + jp * NS + i] += v;
+            }
+        }
+    }
 #pragma unroll
     for (int t = 0; t < NSYM; t++) Sm[t] = Ss[t] = 0.0;
     have = false;
@@ -425,7 +449,7 @@ struct StMatF {
   }
 };
 
-template <int DIM, int ORDER>
+template <int DIM, int ORDER, int NTDR>
 __global__ void __launch_bounds__(128) k_st_elmat(StArgs A, StForm f, int64_t nlist, const int32_t *__restrict__ els, double *__restrict__ out) {
   const int64_t k = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (k >= nlist) return;
@@ -433,7 +457,8 @@ __global__ void __launch_bounds__(128) k_st_elmat(StArgs A, StForm f, int64_t nl
   constexpr int NS = H1<DIM, ORDER>::ND;
   const int N = f.ntd_fe * NS;
   double *blk = out + k * (int64_t)N * N;
-  for (int t = 0; t < N * N; t++) blk[t] = 0.0;
+  if constexpr (NTDR == 0)
+    for (int t = 0; t < N * N; t++) blk[t] = 0.0;
   double p[DIM + 1][DIM];
 #pragma unroll
   for (int m = 0; m <= DIM; m++) {
@@ -451,13 +476,19 @@ __global__ void __launch_bounds__(128) k_st_elmat(StArgs A, StForm f, int64_t nl
     for (int m = 0; m < DIM; m++) { gl[m][d] = G.Jinv[m][d]; sgl += G.Jinv[m][d]; }
     gl[DIM][d] = -sgl;
   }
-  StMatF<DIM, ORDER> F;
+  StMatF<DIM, ORDER, NTDR> F;
   F.gl = gl; F.out = blk; F.f = f; F.meas = fabs(G.det); F.have = false; F.tcur = 0.0;
   st_nodes(f.ntd_fe, F.tnodes);
 #pragma unroll
-  for (int t = 0; t < StMatF<DIM, ORDER>::NSYM; t++) F.Sm[t] = F.Ss[t] = 0.0;
+  for (int t = 0; t < StMatF<DIM, ORDER, NTDR>::NSYM; t++) F.Sm[t] = F.Ss[t] = 0.0;
+#pragma unroll
+  for (int t = 0; t < StMatF<DIM, ORDER, NTDR>::NREG; t++) F.blk[t] = 0.0;
   st_walk<DIM, true>(A, e, F);
   F.flush();
+  if constexpr (NTDR > 0) {
+#pragma unroll
+    for (int t = 0; t < StMatF<DIM, ORDER, NTDR>::NREG; t++) blk[t] = F.blk[t];
+  }
 }
 
 // space-time CutInformation::Update (xfem/cutinfo.cpp:79-111 with time_order >= 0): part "volumes" of the space-time prism from the
@@ -577,10 +608,16 @@ int ngsx_st_elmat_h1(const ngsx_mesh *mesh, const double *lset_st, int ntime_dof
   const unsigned nb = (unsigned)((nlist + 127) / 128);
   cudaStream_t st = as_stream(stream);
   switch (mesh->dim * 10 + fe_order) {
-    case 21: k_st_elmat<2, 1><<<nb, 128, 0, st>>>(A, f, nlist, els, elmats); break;
-    case 22: k_st_elmat<2, 2><<<nb, 128, 0, st>>>(A, f, nlist, els, elmats); break;
-    case 31: k_st_elmat<3, 1><<<nb, 128, 0, st>>>(A, f, nlist, els, elmats); break;
-    case 32: k_st_elmat<3, 2><<<nb, 128, 0, st>>>(A, f, nlist, els, elmats); break;
+    case 21:
+      if (fe_time_dofs == 2) k_st_elmat<2, 1, 2><<<nb, 128, 0, st>>>(A, f, nlist, els, elmats);      // register-resident 6 x 6 block
+      else k_st_elmat<2, 1, 0><<<nb, 128, 0, st>>>(A, f, nlist, els, elmats);
+      break;
+    case 22: k_st_elmat<2, 2, 0><<<nb, 128, 0, st>>>(A, f, nlist, els, elmats); break;
+    case 31:
+      if (fe_time_dofs == 2) k_st_elmat<3, 1, 2><<<nb, 128, 0, st>>>(A, f, nlist, els, elmats);      // 8 x 8
+      else k_st_elmat<3, 1, 0><<<nb, 128, 0, st>>>(A, f, nlist, els, elmats);
+      break;
+    case 32: k_st_elmat<3, 2, 0><<<nb, 128, 0, st>>>(A, f, nlist, els, elmats); break;
   }
   NGSX_LAUNCH_CHECK();
   return NGSX_OK;
